@@ -1,0 +1,383 @@
+// Paged-KV attention for decode / small query counts: split-KV flash-decoding + LSE combine.
+//
+// Reference counterparts: `flash_attn_ext_vec` (llama.cpp/ggml/src/ggml-cuda/fattn-vec.cuh) with
+// `parallel_blocks` split-KV and `flash_attn_combine_results` (fattn-common.cuh:721-772).  The reference
+// cache is a contiguous ring per stream; here K/V live in fixed-size pages
+// [n_pages][Hkv][page_size][D] addressed through a block table, so sequences grow without copies and
+// TP ranks own disjoint KV heads.  One CTA = (split, kv head [x q-head group], query); the G <= 4 query
+// heads that share a KV head are processed together so each K/V byte is read once per group.
+#include "kernels.cuh"
+
+namespace dlp {
+
+template <int D, int G>
+__global__ void __launch_bounds__(128) attn_decode_kernel(const AttnParams p) {
+    constexpr int DL = D / 8;  // dims per lane (8 lanes share one token)
+    static_assert(DL % 8 == 0, "head dim must be a multiple of 64");
+    const int split = blockIdx.x;
+    const int groups_per_kv = (p.Hq / p.Hkv) / G;
+    const int kvh = blockIdx.y / groups_per_kv;
+    const int hq0 = kvh * (p.Hq / p.Hkv) + (blockIdx.y % groups_per_kv) * G;
+    const int qi = blockIdx.z;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int grp = lane >> 3, sub = lane & 7;
+
+    const int len = p.kv_len[qi];
+    const int per = (len + p.n_splits - 1) / p.n_splits;
+    const int begin = split * per, end = min(len, begin + per);
+    const int* bt = p.block_table + (size_t)(p.bt_row ? p.bt_row[qi] : qi) * p.max_pages;
+
+    float q[G][DL];
+#pragma unroll
+    for (int g = 0; g < G; ++g) {
+        const __half* qp = p.q + ((size_t)qi * p.Hq + hq0 + g) * D + sub * DL;
+#pragma unroll
+        for (int i = 0; i < DL; i += 8) {
+            const uint4 v = *reinterpret_cast<const uint4*>(qp + i);
+            const uint32_t w[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                const float2 f = h2_to_f2(w[j]);
+                q[g][i + 2 * j] = f.x;
+                q[g][i + 2 * j + 1] = f.y;
+            }
+        }
+    }
+    float m[G], l[G], o[G][DL];
+#pragma unroll
+    for (int g = 0; g < G; ++g) {
+        m[g] = -INFINITY;
+        l[g] = 0.f;
+#pragma unroll
+        for (int i = 0; i < DL; ++i) o[g][i] = 0.f;
+    }
+
+    // warp-uniform loop bound: all 32 lanes take part in every shuffle; groups past `end` re-read the
+    // last valid token and discard the result
+    for (int tok0 = begin + warp * 4; tok0 < end; tok0 += 16) {
+        const bool valid = tok0 + grp < end;
+        const int tok = valid ? tok0 + grp : end - 1;
+        const int page = bt[tok / p.page_size], off = tok % p.page_size;
+        const size_t base = (((size_t)page * p.Hkv + kvh) * p.page_size + off) * D + sub * DL;
+        float kf[DL], vf[DL];
+#pragma unroll
+        for (int i = 0; i < DL; i += 8) {
+            const uint4 kv = ldg_nc_v4(p.kc + base + i);
+            const uint4 vv = ldg_nc_v4(p.vc + base + i);
+            const uint32_t kw[4] = {kv.x, kv.y, kv.z, kv.w}, vw[4] = {vv.x, vv.y, vv.z, vv.w};
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                const float2 a = h2_to_f2(kw[j]), b = h2_to_f2(vw[j]);
+                kf[i + 2 * j] = a.x; kf[i + 2 * j + 1] = a.y;
+                vf[i + 2 * j] = b.x; vf[i + 2 * j + 1] = b.y;
+            }
+        }
+#pragma unroll
+        for (int g = 0; g < G; ++g) {
+            float s = 0.f;
+#pragma unroll
+            for (int i = 0; i < DL; ++i) s = fmaf(q[g][i], kf[i], s);
+            s += __shfl_xor_sync(0xffffffffu, s, 1);
+            s += __shfl_xor_sync(0xffffffffu, s, 2);
+            s += __shfl_xor_sync(0xffffffffu, s, 4);
+            if (!valid) continue;
+            const float mn = fmaxf(m[g], s);
+            const float alpha = __expf(m[g] - mn), pr = __expf(s - mn);
+            m[g] = mn;
+            l[g] = l[g] * alpha + pr;
+#pragma unroll
+            for (int i = 0; i < DL; ++i) o[g][i] = fmaf(pr, vf[i], o[g][i] * alpha);
+        }
+    }
+    // merge the 4 lane groups of the warp, then the 4 warps of the CTA
+    __shared__ float sm_m[4][G], sm_l[4][G];
+    __shared__ float sm_o[4][G][D];
+#pragma unroll
+    for (int g = 0; g < G; ++g) {
+#pragma unroll
+        for (int off = 8; off <= 16; off <<= 1) {
+            const float m2 = __shfl_xor_sync(0xffffffffu, m[g], off);
+            const float l2 = __shfl_xor_sync(0xffffffffu, l[g], off);
+            const float mn = fmaxf(m[g], m2);
+            const float a1 = (m[g] == -INFINITY) ? 0.f : __expf(m[g] - mn);
+            const float a2 = (m2 == -INFINITY) ? 0.f : __expf(m2 - mn);
+#pragma unroll
+            for (int i = 0; i < DL; ++i) {
+                const float o2 = __shfl_xor_sync(0xffffffffu, o[g][i], off);
+                o[g][i] = o[g][i] * a1 + o2 * a2;
+            }
+            l[g] = l[g] * a1 + l2 * a2;
+            m[g] = mn;
+        }
+        if (grp == 0) {
+#pragma unroll
+            for (int i = 0; i < DL; ++i) sm_o[warp][g][sub * DL + i] = o[g][i];
+            if (sub == 0) { sm_m[warp][g] = m[g]; sm_l[warp][g] = l[g]; }
+        }
+    }
+    __syncthreads();
+    for (int idx = threadIdx.x; idx < G * D; idx += blockDim.x) {
+        const int g = idx / D, d = idx % D;
+        float mn = -INFINITY;
+#pragma unroll
+        for (int w = 0; w < 4; ++w) mn = fmaxf(mn, sm_m[w][g]);
+        float acc = 0.f, ls = 0.f;
+#pragma unroll
+        for (int w = 0; w < 4; ++w) {
+            const float a = (sm_m[w][g] == -INFINITY) ? 0.f : __expf(sm_m[w][g] - mn);
+            acc += sm_o[w][g][d] * a;
+            ls += sm_l[w][g] * a;
+        }
+        const int hq = hq0 + g;
+        if (p.n_splits == 1) {
+            p.out[((size_t)qi * p.Hq + hq) * D + d] = __float2half_rn(ls > 0.f ? acc / ls : 0.f);
+        } else {
+            const size_t pi = ((size_t)qi * p.Hq + hq) * p.n_splits + split;
+            p.part_o[pi * D + d] = acc;
+            if (d == 0) { p.part_ml[pi * 2] = mn; p.part_ml[pi * 2 + 1] = ls; }
+        }
+    }
+}
+
+template <int D>
+__global__ void attn_combine_kernel(const AttnParams p) {
+    const int hq = blockIdx.x, qi = blockIdx.y;
+    const size_t pi0 = ((size_t)qi * p.Hq + hq) * p.n_splits;
+    float mn = -INFINITY;
+    for (int s = 0; s < p.n_splits; ++s) mn = fmaxf(mn, p.part_ml[(pi0 + s) * 2]);
+    for (int d = threadIdx.x; d < D; d += blockDim.x) {
+        float acc = 0.f, ls = 0.f;
+        for (int s = 0; s < p.n_splits; ++s) {
+            const float ms = p.part_ml[(pi0 + s) * 2];
+            const float a = (ms == -INFINITY) ? 0.f : __expf(ms - mn);
+            acc += p.part_o[(pi0 + s) * D + d] * a;
+            ls += p.part_ml[(pi0 + s) * 2 + 1] * a;
+        }
+        p.out[((size_t)qi * p.Hq + hq) * D + d] = __float2half_rn(ls > 0.f ? acc / ls : 0.f);
+    }
+}
+
+template <int D>
+static int launch_attn(const AttnParams& p, cudaStream_t s) {
+    const int gqa = p.Hq / p.Hkv;
+    const int G = gqa % 4 == 0 ? 4 : (gqa % 2 == 0 ? 2 : 1);
+    dim3 grid(p.n_splits, p.Hkv * (gqa / G), p.nq);
+    if (G == 4) attn_decode_kernel<D, 4><<<grid, 128, 0, s>>>(p);
+    else if (G == 2) attn_decode_kernel<D, 2><<<grid, 128, 0, s>>>(p);
+    else attn_decode_kernel<D, 1><<<grid, 128, 0, s>>>(p);
+    DLP_LAUNCH_CHECK();
+    if (p.n_splits > 1) {
+        attn_combine_kernel<D><<<dim3(p.Hq, p.nq), D, 0, s>>>(p);
+        DLP_LAUNCH_CHECK();
+    }
+    return 0;
+}
+
+int attn_paged(const AttnParams& p, int D, cudaStream_t s) {
+    DLP_REQUIRE(p.nq > 0 && p.Hq % p.Hkv == 0, "attn: bad head configuration Hq=%d Hkv=%d", p.Hq, p.Hkv);
+    DLP_REQUIRE(p.n_splits >= 1 && (p.n_splits == 1 || (p.part_o && p.part_ml)), "attn: split-KV needs a workspace");
+    if (D == 64) return launch_attn<64>(p, s);
+    if (D == 128) return launch_attn<128>(p, s);
+    DLP_REQUIRE(false, "attn: head dim %d unsupported (64, 128)", D);
+}
+
+}  // namespace dlp
+
+// =================================================================================================
+// Causal flash-prefill over the paged cache (one sequence chunk).
+//
+// Reference counterpart: `flash_attn_ext_f16` (ggml-cuda/fattn-mma-f16.cuh).  FlashAttention-2 schedule:
+// one CTA = 64 query rows of one head (4 warps x 16 rows), K/V streamed page-by-page through shared
+// memory with cp.async, scores and P.V on the legacy tensor-core path (mma.sync m16n8k16, fp32
+// accumulate), online softmax in registers.  Attention is ~1% of prefill FLOPs at the benchmark shapes
+// (the linear layers run on tcgen05), so this kernel favours simplicity; a TMEM-resident variant is the
+// planned upgrade.
+namespace dlp {
+
+__device__ __forceinline__ void cp_async16(void* smem, const void* gmem, bool pred) {
+    const uint32_t s = smem_u32(smem);
+    const int sz = pred ? 16 : 0;  // src-size 0 => zero fill
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(s), "l"(gmem), "r"(sz) : "memory");
+}
+__device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_all;" ::: "memory"); }
+
+__device__ __forceinline__ void ldmatrix_x4(uint32_t (&r)[4], const void* smem) {
+    asm volatile("ldmatrix.sync.aligned.m8n8.x4.shared.b16 {%0,%1,%2,%3}, [%4];"
+                 : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]) : "r"(smem_u32(smem)));
+}
+__device__ __forceinline__ void ldmatrix_x4_trans(uint32_t (&r)[4], const void* smem) {
+    asm volatile("ldmatrix.sync.aligned.m8n8.x4.trans.shared.b16 {%0,%1,%2,%3}, [%4];"
+                 : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]) : "r"(smem_u32(smem)));
+}
+__device__ __forceinline__ void mma_16816(float (&c)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1) {
+    asm volatile("mma.sync.aligned.m16n8k16.row.col.f32.f16.f16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+                 : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3])
+                 : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
+}
+__device__ __forceinline__ uint32_t pack_h2(float a, float b) {
+    __half2 h = __floats2half2_rn(a, b);
+    return *reinterpret_cast<uint32_t*>(&h);
+}
+
+template <int D>
+__global__ void __launch_bounds__(128) attn_prefill_kernel(const __half* __restrict__ q, const __half* __restrict__ kc,
+                                                           const __half* __restrict__ vc, const int* __restrict__ bt,
+                                                           __half* __restrict__ out, int T, int pos0, int Hq, int Hkv, int PS) {
+    constexpr int LD = D + 8;      // padded row (halves) -> conflict-free ldmatrix
+    constexpr int BQ = 64, BKV = 64;
+    extern __shared__ __align__(16) uint8_t att_smem[];
+    __half* sQ = reinterpret_cast<__half*>(att_smem);
+    __half* sK = sQ + BQ * LD;
+    __half* sV = sK + BKV * LD;
+    const int q0 = blockIdx.x * BQ, hq = blockIdx.y, kvh = hq / (Hq / Hkv);
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int g = lane >> 2, t4 = lane & 3;
+    constexpr int CPR = D / 8;  // 16-byte chunks per row
+
+    for (int i = tid; i < BQ * CPR; i += 128) {
+        const int r = i / CPR, c = i % CPR;
+        const bool ok = q0 + r < T;
+        cp_async16(sQ + r * LD + c * 8, q + ((size_t)(ok ? q0 + r : 0) * Hq + hq) * D + c * 8, ok);
+    }
+    const int n_kv = pos0 + min(q0 + BQ, T);
+    const int n_tiles = (n_kv + BKV - 1) / BKV;
+
+    uint32_t qf[D / 16][4];
+    float o[D / 8][4];
+#pragma unroll
+    for (int i = 0; i < D / 8; ++i) { o[i][0] = o[i][1] = o[i][2] = o[i][3] = 0.f; }
+    float m_run[2] = {-INFINITY, -INFINITY}, l_run[2] = {0.f, 0.f};
+    constexpr float LOG2E = 1.4426950408889634f;
+
+    for (int kt = 0; kt < n_tiles; ++kt) {
+        __syncthreads();  // previous tile fully consumed
+        for (int i = tid; i < BKV * CPR; i += 128) {
+            const int r = i / CPR, c = i % CPR;
+            const int tok = kt * BKV + r;
+            const bool ok = tok < n_kv;
+            const int tk = ok ? tok : 0;
+            const size_t src = (((size_t)bt[tk / PS] * Hkv + kvh) * PS + tk % PS) * D + c * 8;
+            cp_async16(sK + r * LD + c * 8, kc + src, ok);
+            cp_async16(sV + r * LD + c * 8, vc + src, ok);
+        }
+        cp_async_wait_all();
+        __syncthreads();
+        if (kt == 0) {
+#pragma unroll
+            for (int ks = 0; ks < D / 16; ++ks)
+                ldmatrix_x4(qf[ks], sQ + (warp * 16 + (lane & 15)) * LD + ks * 16 + (lane >> 4) * 8);
+        }
+        // ---- S = Q K^T (16 x 64 per warp) ----
+        float s[BKV / 8][4];
+#pragma unroll
+        for (int i = 0; i < BKV / 8; ++i) { s[i][0] = s[i][1] = s[i][2] = s[i][3] = 0.f; }
+#pragma unroll
+        for (int ks = 0; ks < D / 16; ++ks) {
+#pragma unroll
+            for (int np = 0; np < BKV / 16; ++np) {
+                uint32_t kb[4];
+                const int mat = lane >> 3, r = lane & 7;
+                ldmatrix_x4(kb, sK + (np * 16 + (mat >> 1) * 8 + r) * LD + ks * 16 + (mat & 1) * 8);
+                mma_16816(s[np * 2], qf[ks], kb[0], kb[1]);
+                mma_16816(s[np * 2 + 1], qf[ks], kb[2], kb[3]);
+            }
+        }
+        // ---- causal mask + online softmax (rows g and g+8 of this warp's 16) ----
+        const int qpos0 = pos0 + q0 + warp * 16 + g;
+        float mx[2] = {-INFINITY, -INFINITY};
+#pragma unroll
+        for (int nt = 0; nt < BKV / 8; ++nt) {
+#pragma unroll
+            for (int e = 0; e < 4; ++e) {
+                const int kpos = kt * BKV + nt * 8 + t4 * 2 + (e & 1);
+                const int qpos = qpos0 + (e >> 1) * 8;
+                if (kpos > qpos) s[nt][e] = -INFINITY;
+                mx[e >> 1] = fmaxf(mx[e >> 1], s[nt][e]);
+            }
+        }
+        float alpha[2], msc[2];
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+            mx[h] = fmaxf(mx[h], __shfl_xor_sync(0xffffffffu, mx[h], 1));
+            mx[h] = fmaxf(mx[h], __shfl_xor_sync(0xffffffffu, mx[h], 2));
+            const float mn = fmaxf(m_run[h], mx[h]);
+            alpha[h] = (m_run[h] == -INFINITY) ? 0.f : exp2f((m_run[h] - mn) * LOG2E);
+            msc[h] = (mn == -INFINITY) ? 0.f : mn * LOG2E;
+            m_run[h] = mn;
+        }
+        float rs[2] = {0.f, 0.f};
+#pragma unroll
+        for (int nt = 0; nt < BKV / 8; ++nt) {
+#pragma unroll
+            for (int e = 0; e < 4; ++e) {
+                const float pv = exp2f(s[nt][e] * LOG2E - msc[e >> 1]);  // exp2(-inf) = 0 for masked keys
+                s[nt][e] = pv;
+                rs[e >> 1] += pv;
+            }
+        }
+#pragma unroll
+        for (int h = 0; h < 2; ++h) l_run[h] = l_run[h] * alpha[h] + rs[h];
+#pragma unroll
+        for (int i = 0; i < D / 8; ++i) {
+            o[i][0] *= alpha[0]; o[i][1] *= alpha[0];
+            o[i][2] *= alpha[1]; o[i][3] *= alpha[1];
+        }
+        // ---- O += P V ----
+#pragma unroll
+        for (int kk = 0; kk < BKV / 16; ++kk) {
+            uint32_t pa[4];
+            pa[0] = pack_h2(s[2 * kk][0], s[2 * kk][1]);
+            pa[1] = pack_h2(s[2 * kk][2], s[2 * kk][3]);
+            pa[2] = pack_h2(s[2 * kk + 1][0], s[2 * kk + 1][1]);
+            pa[3] = pack_h2(s[2 * kk + 1][2], s[2 * kk + 1][3]);
+#pragma unroll
+            for (int dp = 0; dp < D / 16; ++dp) {
+                uint32_t vb[4];
+                const int mat = lane >> 3, r = lane & 7;
+                ldmatrix_x4_trans(vb, sV + (kk * 16 + (mat & 1) * 8 + r) * LD + dp * 16 + (mat >> 1) * 8);
+                mma_16816(o[dp * 2], pa, vb[0], vb[1]);
+                mma_16816(o[dp * 2 + 1], pa, vb[2], vb[3]);
+            }
+        }
+    }
+    // ---- finalise: row sums live per-quad; reduce then normalise and store ----
+#pragma unroll
+    for (int h = 0; h < 2; ++h) {
+        l_run[h] += __shfl_xor_sync(0xffffffffu, l_run[h], 1);
+        l_run[h] += __shfl_xor_sync(0xffffffffu, l_run[h], 2);
+    }
+#pragma unroll
+    for (int h = 0; h < 2; ++h) {
+        const int row = q0 + warp * 16 + g + h * 8;
+        if (row < T) {
+            const float inv = l_run[h] > 0.f ? 1.f / l_run[h] : 0.f;
+            __half* op = out + ((size_t)row * Hq + hq) * D;
+#pragma unroll
+            for (int i = 0; i < D / 8; ++i) {
+                const uint32_t v = pack_h2(o[i][h * 2] * inv, o[i][h * 2 + 1] * inv);
+                *reinterpret_cast<uint32_t*>(op + i * 8 + t4 * 2) = v;
+            }
+        }
+    }
+}
+
+int attn_prefill(const __half* q, const __half* kc, const __half* vc, const int* bt_row, __half* out, int T, int pos0,
+                 int Hq, int Hkv, int D, int page_size, cudaStream_t s) {
+    DLP_REQUIRE(T > 0 && Hq % Hkv == 0, "attn_prefill: bad shape");
+    dim3 grid((T + 63) / 64, Hq);
+    if (D == 128) {
+        const int smem = 3 * 64 * (128 + 8) * 2;
+        static bool cfg = false;
+        if (!cfg) { DLP_CHECK_CUDA(cudaFuncSetAttribute(attn_prefill_kernel<128>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem)); cfg = true; }
+        attn_prefill_kernel<128><<<grid, 128, smem, s>>>(q, kc, vc, bt_row, out, T, pos0, Hq, Hkv, page_size);
+    } else if (D == 64) {
+        const int smem = 3 * 64 * (64 + 8) * 2;
+        attn_prefill_kernel<64><<<grid, 128, smem, s>>>(q, kc, vc, bt_row, out, T, pos0, Hq, Hkv, page_size);
+    } else {
+        DLP_REQUIRE(false, "attn_prefill: head dim %d unsupported (64, 128)", D);
+    }
+    DLP_LAUNCH_CHECK();
+    return 0;
+}
+
+}  // namespace dlp

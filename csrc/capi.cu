@@ -1,0 +1,163 @@
+// extern "C" surface of libdlp_b200.so (declarations: include/dlp_b200.h).
+#include <stdarg.h>
+#include <string.h>
+
+#include "../include/dlp_b200.h"
+#include "kernels.cuh"
+
+namespace dlp {
+
+static thread_local char g_err[512] = "";
+
+void set_error(const char* fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof(g_err), fmt, ap);
+    va_end(ap);
+}
+const char* get_error() { return g_err; }
+
+int sm_count() {
+    static int cached[64] = {0};
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return 148;
+    if (cached[dev] == 0) {
+        int n = 0;
+        if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n <= 0) n = 148;
+        cached[dev] = n;
+    }
+    return cached[dev];
+}
+
+static QWeight to_qw(const dlp_weight* w) {
+    QWeight q;
+    q.base = (const uint8_t*)w->base;
+    q.aux0 = (const uint8_t*)w->aux0;
+    q.aux1 = (const uint8_t*)w->aux1;
+    q.aux2 = (const uint8_t*)w->aux2;
+    q.N = w->N;
+    q.K = w->K;
+    return q;
+}
+
+}  // namespace dlp
+
+using namespace dlp;
+
+extern "C" {
+
+const char* dlp_last_error(void) { return get_error(); }
+int dlp_version(void) { return 100; }
+int dlp_sm_count(void) { return sm_count(); }
+
+int dlp_gemv(const dlp_weight* w0, const dlp_weight* w1, const void* x, const float* norm_w, float eps, void* y,
+             int ldy, int out_mode, int T, void* stream) {
+    DLP_REQUIRE(w0 && w0->base && x && y, "dlp_gemv: null argument");
+    DLP_REQUIRE(!w1 || (w1->wtype == w0->wtype && w1->N == w0->N && w1->K == w0->K), "dlp_gemv: gate/up mismatch");
+    GemvParams p;
+    memset(&p, 0, sizeof(p));
+    p.w0 = to_qw(w0);
+    if (w1) p.w1 = to_qw(w1);
+    p.x = x; p.norm_w = norm_w; p.eps = eps; p.y = y; p.ldy = ldy; p.out_mode = out_mode; p.T = T;
+    return gemv(p, w0->wtype, (cudaStream_t)stream);
+}
+
+int dlp_gemm_f16(const void* w0, const void* w1, int ldw, const void* x, int ldx, void* y, int ldy, int T, int N,
+                 int K, int epilogue, int is_bf16, int split_k, void* stream) {
+    DLP_REQUIRE(w0 && x && y, "dlp_gemm_f16: null argument");
+    return gemm_f16(w0, w1, ldw, x, ldx, y, ldy, T, N, K, epilogue, is_bf16, split_k, (cudaStream_t)stream);
+}
+
+int dlp_linear(const dlp_weight* w0, const dlp_weight* w1, const void* x, const float* norm_w, float eps, void* y,
+               int ldy, int out_mode, int T, void* scratch, size_t scratch_bytes, void* stream) {
+    DLP_REQUIRE(w0 && w0->base && x && y, "dlp_linear: null argument");
+    if (T == 1 || T == 2 || T == 4) return dlp_gemv(w0, w1, x, norm_w, eps, y, ldy, out_mode, T, stream);
+    DLP_REQUIRE(norm_w == nullptr, "dlp_linear: RMSNorm fusion is only available on the T<=4 mat-vec path");
+    const int epi = out_mode == DLP_OUT_F16 ? 0 : out_mode == DLP_OUT_F32 ? 1 : out_mode == DLP_OUT_ADD_F32 ? 2 : 3;
+    const int wt = w0->wtype;
+    cudaStream_t s = (cudaStream_t)stream;
+    if (wt == DLP_W_F16 || wt == DLP_W_BF16)
+        return gemm_f16(w0->base, w1 ? w1->base : nullptr, w0->K, x, w0->K, y, ldy, T, w0->N, w0->K, epi,
+                        wt == DLP_W_BF16, 0, s);
+    // block-quantised: decode to fp16 scratch, then the dense tensor-core GEMM
+    const size_t per = (size_t)w0->N * w0->K * 2;
+    const size_t need = per * (w1 ? 2 : 1);
+    DLP_REQUIRE(scratch != nullptr && scratch_bytes >= need, "dlp_linear: scratch too small (%zu < %zu bytes)", scratch_bytes, need);
+    int rc = dequant_rows_f16(to_qw(w0), wt, nullptr, w0->N, (__half*)scratch, w0->K, s);
+    if (rc) return rc;
+    const void* up = nullptr;
+    if (w1) {
+        up = (const uint8_t*)scratch + per;
+        rc = dequant_rows_f16(to_qw(w1), wt, nullptr, w1->N, (__half*)up, w1->K, s);
+        if (rc) return rc;
+    }
+    return gemm_f16(scratch, up, w0->K, x, w0->K, y, ldy, T, w0->N, w0->K, epi, 0, 0, s);
+}
+
+int dlp_dequant_rows_f32(const dlp_weight* w, const int32_t* row_ids, int n_rows, float* out, int ld_out, void* stream) {
+    DLP_REQUIRE(w && w->base && out, "dlp_dequant_rows_f32: null argument");
+    return dequant_rows_f32(to_qw(w), w->wtype, row_ids, n_rows, out, ld_out, (cudaStream_t)stream);
+}
+int dlp_dequant_rows_f16(const dlp_weight* w, const int32_t* row_ids, int n_rows, void* out, int ld_out, void* stream) {
+    DLP_REQUIRE(w && w->base && out, "dlp_dequant_rows_f16: null argument");
+    return dequant_rows_f16(to_qw(w), w->wtype, row_ids, n_rows, (__half*)out, ld_out, (cudaStream_t)stream);
+}
+
+int dlp_rmsnorm(float* h, const float* delta, const float* w, void* out_f16, int T, int E, float eps, void* stream) {
+    DLP_REQUIRE(h && (w || !out_f16), "dlp_rmsnorm: null argument");
+    return rmsnorm(h, delta, w, (__half*)out_f16, T, E, eps, (cudaStream_t)stream);
+}
+
+int dlp_rope_kv(const void* qkv, int qkv_is_f16, const int32_t* pos, const int32_t* slot, const float* inv_freq,
+                void* q_out, void* k_cache, void* v_cache, int T, int Hq, int Hkv, int D, int n_rot, int page_size,
+                int neox, float q_scale, void* stream) {
+    DLP_REQUIRE(qkv && pos && slot && inv_freq && q_out && k_cache && v_cache, "dlp_rope_kv: null argument");
+    return rope_kv(qkv, qkv_is_f16, pos, slot, inv_freq, (__half*)q_out, (__half*)k_cache, (__half*)v_cache, T, Hq, Hkv,
+                   D, n_rot, page_size, neox, q_scale, (cudaStream_t)stream);
+}
+
+int dlp_swiglu(const void* gate_up, int is_f16, void* out_f16, int T, int F, int ld_in, void* stream) {
+    DLP_REQUIRE(gate_up && out_f16, "dlp_swiglu: null argument");
+    return swiglu(gate_up, is_f16, (__half*)out_f16, T, F, ld_in, (cudaStream_t)stream);
+}
+
+int dlp_advance(int32_t* seq_len, int32_t* pos, int32_t* slot, const int32_t* block_table, int max_pages,
+                int page_size, int n, void* stream) {
+    DLP_REQUIRE(seq_len && pos && slot && block_table && n > 0, "dlp_advance: bad argument");
+    return advance(seq_len, pos, slot, block_table, max_pages, page_size, n, (cudaStream_t)stream);
+}
+
+int dlp_attn_paged(const void* q, const void* k_cache, const void* v_cache, const int32_t* block_table,
+                   const int32_t* bt_row, const int32_t* kv_len, void* out, float* part_o, float* part_ml, int nq,
+                   int Hq, int Hkv, int D, int max_pages, int page_size, int n_splits, void* stream) {
+    DLP_REQUIRE(q && k_cache && v_cache && block_table && kv_len && out, "dlp_attn_paged: null argument");
+    AttnParams p;
+    p.q = (const __half*)q; p.kc = (const __half*)k_cache; p.vc = (const __half*)v_cache;
+    p.block_table = block_table; p.bt_row = bt_row; p.kv_len = kv_len; p.out = (__half*)out;
+    p.part_o = part_o; p.part_ml = part_ml;
+    p.nq = nq; p.Hq = Hq; p.Hkv = Hkv; p.max_pages = max_pages; p.page_size = page_size; p.n_splits = n_splits;
+    return attn_paged(p, D, (cudaStream_t)stream);
+}
+
+int dlp_attn_prefill(const void* q, const void* k_cache, const void* v_cache, const int32_t* block_table_row,
+                     void* out, int T, int pos0, int Hq, int Hkv, int D, int page_size, void* stream) {
+    DLP_REQUIRE(q && k_cache && v_cache && block_table_row && out, "dlp_attn_prefill: null argument");
+    return attn_prefill((const __half*)q, (const __half*)k_cache, (const __half*)v_cache, block_table_row, (__half*)out,
+                        T, pos0, Hq, Hkv, D, page_size, (cudaStream_t)stream);
+}
+
+int dlp_argmax(const float* logits, int R, int V, int ld, int32_t* out, void* stream) {
+    DLP_REQUIRE(logits && out, "dlp_argmax: null argument");
+    return argmax(logits, R, V, ld, out, (cudaStream_t)stream);
+}
+int dlp_sample(const float* logits, int R, int V, int ld, int top_k, float top_p, float min_p, float temp,
+               uint32_t seed, const int32_t* step_ctr, int32_t* out, void* stream) {
+    DLP_REQUIRE(logits && out, "dlp_sample: null argument");
+    return sample(logits, R, V, ld, top_k, top_p, min_p, temp, seed, step_ctr, out, (cudaStream_t)stream);
+}
+int dlp_f32_to_f16(const float* in, void* out, size_t n, void* stream) {
+    DLP_REQUIRE(in && out, "dlp_f32_to_f16: null argument");
+    return f32_to_f16(in, (__half*)out, n, (cudaStream_t)stream);
+}
+
+}  // extern "C"

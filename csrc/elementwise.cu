@@ -1,0 +1,375 @@
+// Small fused ops around the GEMMs: embedding gather (+dequant), RMSNorm (+residual), RoPE fused with
+// the paged-KV write, SwiGLU, dequant-to-fp16, sampling.
+//
+// Reference counterparts (llama.cpp/ggml/src/ggml-cuda/): getrows.cu, norm.cu:107 (fused x weight + residual),
+// rope.cu:44-111 with the set_rows fusion (:58-78), set-rows.cu, unary.cu (GLU), convert.cu, argmax.cu.
+// The sampler chain order follows common/sampling.cpp (top-k -> top-p -> min-p -> temperature -> dist) but runs
+// on the device so only the chosen token id crosses PCIe.
+#include "kernels.cuh"
+
+namespace dlp {
+
+// ---------------------------------------------------------------------------------------------
+// generic "decode 16 consecutive elements of a row" used by embedding gather and dequant-to-fp16
+template <int WT>
+__device__ __forceinline__ void decode_chunk_to_f32(const QWeight& w, int row, int c, float* out32, int* k0, int* k1) {
+    QChunk ch;
+    load_chunk<WT>(w, row, c, ch);
+#pragma unroll
+    for (int g = 0; g < 2; ++g)
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+            const float2 f = __half22float2(ch.q[g][i]);
+            out32[g * 16 + i * 2] = fmaf(ch.scale[g], f.x, ch.bias[g]);
+            out32[g * 16 + i * 2 + 1] = fmaf(ch.scale[g], f.y, ch.bias[g]);
+        }
+    *k0 = ch.k[0];
+    *k1 = ch.k[1];
+}
+
+template <int WT, typename OutT>
+__global__ void dequant_rows_kernel(const QWeight w, const int* __restrict__ row_ids, OutT* __restrict__ out, int ld_out) {
+    // grid.x = output rows; each thread decodes 32-element chunks
+    const int orow = blockIdx.x;
+    const int row = row_ids ? row_ids[orow] : orow;
+    const int nchunk = w.K / 32;
+    for (int c = threadIdx.x; c < nchunk; c += blockDim.x) {
+        float v[32];
+        int k0, k1;
+        decode_chunk_to_f32<WT>(w, row, c, v, &k0, &k1);
+        OutT* o = out + (size_t)orow * ld_out;
+#pragma unroll
+        for (int i = 0; i < 16; ++i) {
+            o[k0 + i] = (OutT)v[i];
+            o[k1 + i] = (OutT)v[16 + i];
+        }
+    }
+}
+
+template <typename InT, typename OutT>
+__global__ void dense_rows_kernel(const InT* __restrict__ w, int K, const int* __restrict__ row_ids, OutT* __restrict__ out, int ld_out) {
+    const int orow = blockIdx.x;
+    const int row = row_ids ? row_ids[orow] : orow;
+    for (int k = threadIdx.x; k < K; k += blockDim.x) out[(size_t)orow * ld_out + k] = (OutT)(float)w[(size_t)row * K + k];
+}
+
+template <typename OutT>
+static int dequant_rows_t(const QWeight& w, int wtype, const int* row_ids, int n_rows, OutT* out, int ld_out, cudaStream_t s) {
+    DLP_REQUIRE(n_rows > 0, "dequant_rows: no rows");
+    const int threads = 128;
+    switch (wtype) {
+        case W_F16: dense_rows_kernel<__half, OutT><<<n_rows, 256, 0, s>>>((const __half*)w.base, w.K, row_ids, out, ld_out); break;
+        case W_BF16: dense_rows_kernel<__nv_bfloat16, OutT><<<n_rows, 256, 0, s>>>((const __nv_bfloat16*)w.base, w.K, row_ids, out, ld_out); break;
+        case W_F32: dense_rows_kernel<float, OutT><<<n_rows, 256, 0, s>>>((const float*)w.base, w.K, row_ids, out, ld_out); break;
+        case W_Q8_0: dequant_rows_kernel<W_Q8_0, OutT><<<n_rows, threads, 0, s>>>(w, row_ids, out, ld_out); break;
+        case W_Q4_K: dequant_rows_kernel<W_Q4_K, OutT><<<n_rows, threads, 0, s>>>(w, row_ids, out, ld_out); break;
+        case W_Q5_K: dequant_rows_kernel<W_Q5_K, OutT><<<n_rows, threads, 0, s>>>(w, row_ids, out, ld_out); break;
+        case W_Q6_K: dequant_rows_kernel<W_Q6_K, OutT><<<n_rows, threads, 0, s>>>(w, row_ids, out, ld_out); break;
+        default: DLP_REQUIRE(false, "dequant_rows: unsupported weight type %d", wtype);
+    }
+    DLP_LAUNCH_CHECK();
+    return 0;
+}
+
+int dequant_rows_f32(const QWeight& w, int wtype, const int* row_ids, int n_rows, float* out, int ld_out, cudaStream_t s) {
+    return dequant_rows_t<float>(w, wtype, row_ids, n_rows, out, ld_out, s);
+}
+int dequant_rows_f16(const QWeight& w, int wtype, const int* row_ids, int n_rows, __half* out, int ld_out, cudaStream_t s) {
+    return dequant_rows_t<__half>(w, wtype, row_ids, n_rows, out, ld_out, s);
+}
+
+// ---------------------------------------------------------------------------------------------
+// RMSNorm:  h (fp32) [+= delta]  ->  out fp16 = h * rsqrt(mean(h^2) + eps) * w
+__global__ void __launch_bounds__(256) rmsnorm_kernel(float* __restrict__ h, const float* __restrict__ delta,
+                                                      const float* __restrict__ w, __half* __restrict__ out, int E, float eps) {
+    __shared__ float red[32];
+    const size_t base = (size_t)blockIdx.x * E;
+    float ss = 0.f;
+    for (int k = threadIdx.x * 4; k < E; k += blockDim.x * 4) {
+        float4 v = *reinterpret_cast<const float4*>(h + base + k);
+        if (delta) {
+            const float4 d = *reinterpret_cast<const float4*>(delta + base + k);
+            v.x += d.x; v.y += d.y; v.z += d.z; v.w += d.w;
+            *reinterpret_cast<float4*>(h + base + k) = v;
+        }
+        ss += v.x * v.x + v.y * v.y + v.z * v.z + v.w * v.w;
+    }
+    ss = block_sum(ss, red);
+    const float rs = rsqrtf(ss / (float)E + eps);
+    if (out == nullptr) return;
+    for (int k = threadIdx.x * 4; k < E; k += blockDim.x * 4) {
+        const float4 v = *reinterpret_cast<const float4*>(h + base + k);
+        const float4 g = *reinterpret_cast<const float4*>(w + k);
+        __half2 a = __floats2half2_rn(v.x * rs * g.x, v.y * rs * g.y);
+        __half2 b = __floats2half2_rn(v.z * rs * g.z, v.w * rs * g.w);
+        uint2 o;
+        o.x = *reinterpret_cast<uint32_t*>(&a);
+        o.y = *reinterpret_cast<uint32_t*>(&b);
+        *reinterpret_cast<uint2*>(out + base + k) = o;
+    }
+}
+
+int rmsnorm(float* h, const float* delta, const float* w, __half* out, int T, int E, float eps, cudaStream_t s) {
+    DLP_REQUIRE(E % 4 == 0 && T > 0, "rmsnorm: bad shape T=%d E=%d", T, E);
+    rmsnorm_kernel<<<T, 256, 0, s>>>(h, delta, w, out, E, eps);
+    DLP_LAUNCH_CHECK();
+    return 0;
+}
+
+// ---------------------------------------------------------------------------------------------
+// RoPE (adjacent-pair "norm" or half-split "neox") on Q and K, fused with the paged-KV write of K and V.
+//   qkv   : [T, (Hq + 2*Hkv) * D]  fp32 or fp16 (row = q heads | k heads | v heads)
+//   q_out : [T, Hq * D] fp16 (rotated, pre-scaled by q_scale)
+//   k/v cache : [n_pages][Hkv][page_size][D] fp16 ; slot[t] = page * page_size + offset   (slot < 0 => skip write)
+template <typename InT>
+__global__ void rope_kv_kernel(const InT* __restrict__ qkv, const int* __restrict__ pos, const int* __restrict__ slot,
+                               const float* __restrict__ inv_freq, __half* __restrict__ q_out, __half* __restrict__ kc,
+                               __half* __restrict__ vc, int Hq, int Hkv, int D, int n_rot, int page_size, int neox, float q_scale) {
+    const int t = blockIdx.x;
+    const int H = Hq + 2 * Hkv;
+    const float p = (float)pos[t];
+    const int sl = slot[t];
+    const int page = sl >= 0 ? sl / page_size : 0, off = sl >= 0 ? sl % page_size : 0;
+    const InT* row = qkv + (size_t)t * H * D;
+    const int half_d = D / 2;
+    for (int idx = threadIdx.x; idx < H * half_d; idx += blockDim.x) {
+        const int hh = idx / half_d, i = idx % half_d;
+        int d0, d1;
+        if (neox) { d0 = i; d1 = i + n_rot / 2; } else { d0 = 2 * i; d1 = 2 * i + 1; }
+        const bool rot = hh < Hq + Hkv && (neox ? i < n_rot / 2 : 2 * i < n_rot);
+        if (neox && !rot && i >= n_rot / 2) {  // tail dims beyond the rotated span: map pair index onto them
+            d0 = n_rot + 2 * (i - n_rot / 2);
+            d1 = d0 + 1;
+        }
+        float x0 = (float)row[hh * D + d0], x1 = (float)row[hh * D + d1];
+        if (rot) {
+            float sn, cs;
+            sincosf(p * inv_freq[i], &sn, &cs);
+            const float r0 = x0 * cs - x1 * sn, r1 = x0 * sn + x1 * cs;
+            x0 = r0; x1 = r1;
+        }
+        if (hh < Hq) {
+            __half* o = q_out + ((size_t)t * Hq + hh) * D;
+            o[d0] = __float2half_rn(x0 * q_scale);
+            o[d1] = __float2half_rn(x1 * q_scale);
+        } else if (sl >= 0) {
+            const bool is_k = hh < Hq + Hkv;
+            const int kvh = is_k ? hh - Hq : hh - Hq - Hkv;
+            __half* o = (is_k ? kc : vc) + (((size_t)page * Hkv + kvh) * page_size + off) * D;
+            o[d0] = __float2half_rn(x0);
+            o[d1] = __float2half_rn(x1);
+        }
+    }
+}
+
+int rope_kv(const void* qkv, int qkv_is_f16, const int* pos, const int* slot, const float* inv_freq, __half* q_out,
+            __half* kc, __half* vc, int T, int Hq, int Hkv, int D, int n_rot, int page_size, int neox, float q_scale,
+            cudaStream_t s) {
+    DLP_REQUIRE(T > 0 && D % 2 == 0 && n_rot <= D && n_rot % 2 == 0, "rope_kv: bad shape");
+    if (qkv_is_f16)
+        rope_kv_kernel<__half><<<T, 256, 0, s>>>((const __half*)qkv, pos, slot, inv_freq, q_out, kc, vc, Hq, Hkv, D, n_rot, page_size, neox, q_scale);
+    else
+        rope_kv_kernel<float><<<T, 256, 0, s>>>((const float*)qkv, pos, slot, inv_freq, q_out, kc, vc, Hq, Hkv, D, n_rot, page_size, neox, q_scale);
+    DLP_LAUNCH_CHECK();
+    return 0;
+}
+
+// ---------------------------------------------------------------------------------------------
+// SwiGLU on a fused [T, 2F] (gate | up) fp16/fp32 buffer -> fp16 [T, F]
+template <typename InT>
+__global__ void swiglu_kernel(const InT* __restrict__ gu, __half* __restrict__ out, int F, int ld_in) {
+    const int t = blockIdx.y;
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < F) {
+        const float g = (float)gu[(size_t)t * ld_in + i], u = (float)gu[(size_t)t * ld_in + F + i];
+        out[(size_t)t * F + i] = __float2half_rn(g / (1.f + __expf(-g)) * u);
+    }
+}
+int swiglu(const void* gu, int is_f16, __half* out, int T, int F, int ld_in, cudaStream_t s) {
+    dim3 grid((F + 255) / 256, T);
+    if (is_f16) swiglu_kernel<__half><<<grid, 256, 0, s>>>((const __half*)gu, out, F, ld_in);
+    else swiglu_kernel<float><<<grid, 256, 0, s>>>((const float*)gu, out, F, ld_in);
+    DLP_LAUNCH_CHECK();
+    return 0;
+}
+
+// ---------------------------------------------------------------------------------------------
+// decode bookkeeping on the device (keeps the per-token loop free of host round trips):
+//   pos[s] = seq_len[s]; slot[s] = block_table[s][pos / page] * page + pos % page; seq_len[s] += 1
+__global__ void advance_kernel(int* __restrict__ seq_len, int* __restrict__ pos, int* __restrict__ slot,
+                               const int* __restrict__ block_table, int max_pages, int page_size, int n) {
+    const int s = blockIdx.x * blockDim.x + threadIdx.x;
+    if (s >= n) return;
+    const int p = seq_len[s];
+    pos[s] = p;
+    const int pg = p / page_size;
+    slot[s] = (pg < max_pages) ? block_table[(size_t)s * max_pages + pg] * page_size + p % page_size : -1;
+    seq_len[s] = p + 1;
+}
+int advance(int* seq_len, int* pos, int* slot, const int* block_table, int max_pages, int page_size, int n, cudaStream_t s) {
+    advance_kernel<<<(n + 127) / 128, 128, 0, s>>>(seq_len, pos, slot, block_table, max_pages, page_size, n);
+    DLP_LAUNCH_CHECK();
+    return 0;
+}
+
+// ---------------------------------------------------------------------------------------------
+// Sampling.  One CTA per row of logits [R, V] (fp32).
+__device__ __forceinline__ uint32_t hash_u32(uint32_t x) {
+    x ^= x >> 16; x *= 0x7feb352dU; x ^= x >> 15; x *= 0x846ca68bU; x ^= x >> 16;
+    return x;
+}
+__device__ __forceinline__ uint32_t f2ord(float f) {  // order-preserving float -> uint
+    const uint32_t u = __float_as_uint(f);
+    return (u & 0x80000000u) ? ~u : (u | 0x80000000u);
+}
+
+__global__ void __launch_bounds__(1024) argmax_kernel(const float* __restrict__ logits, int V, int ld, int* __restrict__ out) {
+    __shared__ float sv[32];
+    __shared__ int si[32];
+    const float* row = logits + (size_t)blockIdx.x * ld;
+    float best = -INFINITY;
+    int bi = 0;
+    for (int i = threadIdx.x; i < V; i += blockDim.x) {
+        const float v = row[i];
+        if (v > best) { best = v; bi = i; }
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        const float ov = __shfl_xor_sync(0xffffffffu, best, o);
+        const int oi = __shfl_xor_sync(0xffffffffu, bi, o);
+        if (ov > best || (ov == best && oi < bi)) { best = ov; bi = oi; }
+    }
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    if (lane == 0) { sv[warp] = best; si[warp] = bi; }
+    __syncthreads();
+    if (warp == 0) {
+        const int nw = blockDim.x >> 5;
+        best = lane < nw ? sv[lane] : -INFINITY;
+        bi = lane < nw ? si[lane] : 0x7fffffff;
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            const float ov = __shfl_xor_sync(0xffffffffu, best, o);
+            const int oi = __shfl_xor_sync(0xffffffffu, bi, o);
+            if (ov > best || (ov == best && oi < bi)) { best = ov; bi = oi; }
+        }
+        if (lane == 0) out[blockIdx.x] = bi;
+    }
+}
+
+int argmax(const float* logits, int R, int V, int ld, int* out, cudaStream_t s) {
+    DLP_REQUIRE(R > 0 && V > 0, "argmax: bad shape");
+    argmax_kernel<<<R, 1024, 0, s>>>(logits, V, ld, out);
+    DLP_LAUNCH_CHECK();
+    return 0;
+}
+
+constexpr int SAMPLE_MAX_CAND = 1024;
+
+// top-k -> top-p -> min-p -> temperature -> multinomial draw
+__global__ void __launch_bounds__(1024) sample_kernel(const float* __restrict__ logits, int V, int ld, int top_k, float top_p,
+                                                      float min_p, float temp, uint32_t seed, const int* __restrict__ step_ctr,
+                                                      int* __restrict__ out) {
+    __shared__ int s_count;
+    __shared__ uint32_t s_lo, s_hi;
+    __shared__ float cv[SAMPLE_MAX_CAND];
+    __shared__ int ci[SAMPLE_MAX_CAND];
+    __shared__ int s_n;
+    const float* row = logits + (size_t)blockIdx.x * ld;
+    const int k = max(1, min(top_k <= 0 ? SAMPLE_MAX_CAND : top_k, min(V, SAMPLE_MAX_CAND)));
+    // bisection on the order-preserving integer image of the logits for the k-th largest value
+    if (threadIdx.x == 0) { s_lo = 0u; s_hi = 0xffffffffu; }
+    __syncthreads();
+    for (int it = 0; it < 32; ++it) {
+        const uint32_t lo = s_lo, hi = s_hi;
+        if (lo >= hi) break;
+        const uint32_t mid = lo + (uint32_t)(((uint64_t)hi - lo + 1) >> 1);
+        if (threadIdx.x == 0) s_count = 0;
+        __syncthreads();
+        int c = 0;
+        for (int i = threadIdx.x; i < V; i += blockDim.x) c += f2ord(row[i]) >= mid;
+        c = (int)warp_sum((float)c);
+        if ((threadIdx.x & 31) == 0 && c) atomicAdd(&s_count, c);
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            if (s_count >= k) s_lo = mid; else s_hi = mid - 1;
+        }
+        __syncthreads();
+    }
+    const uint32_t thr = s_lo;  // largest threshold with count(>= thr) >= k
+    if (threadIdx.x == 0) s_n = 0;
+    __syncthreads();
+    for (int i = threadIdx.x; i < V; i += blockDim.x) {
+        const float v = row[i];
+        if (f2ord(v) >= thr) {
+            const int slot = atomicAdd(&s_n, 1);
+            if (slot < SAMPLE_MAX_CAND) { cv[slot] = v; ci[slot] = i; }
+        }
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        int n = min(s_n, SAMPLE_MAX_CAND);
+        // small insertion sort, descending by (value, -index) for determinism
+        for (int a = 1; a < n; ++a) {
+            const float v = cv[a]; const int id = ci[a];
+            int b = a - 1;
+            while (b >= 0 && (cv[b] < v || (cv[b] == v && ci[b] > id))) { cv[b + 1] = cv[b]; ci[b + 1] = ci[b]; --b; }
+            cv[b + 1] = v; ci[b + 1] = id;
+        }
+        if (n > k) n = k;  // ties at the threshold
+        const float mx = cv[0];
+        float sum = 0.f;
+        for (int a = 0; a < n; ++a) sum += __expf(cv[a] - mx);
+        // top-p (keep the smallest prefix with cumulative prob >= top_p), then min-p relative to the best
+        if (top_p < 1.f) {
+            float cum = 0.f;
+            int keep = n;
+            for (int a = 0; a < n; ++a) {
+                cum += __expf(cv[a] - mx) / sum;
+                if (cum >= top_p) { keep = a + 1; break; }
+            }
+            n = keep;
+        }
+        if (min_p > 0.f) {
+            int keep = 1;
+            for (int a = 1; a < n; ++a) if (__expf(cv[a] - mx) >= min_p) keep = a + 1; else break;
+            n = keep;
+        }
+        int choice = 0;
+        if (temp > 0.f && n > 1) {
+            float z = 0.f;
+            for (int a = 0; a < n; ++a) z += __expf((cv[a] - mx) / temp);
+            const uint32_t ctr = step_ctr ? (uint32_t)step_ctr[0] : 0u;
+            const uint32_t r = hash_u32(seed ^ hash_u32(ctr * 0x9E3779B9u + blockIdx.x + 0x85ebca6bu));
+            const float u = (float)(r >> 8) * (1.0f / 16777216.0f) * z;
+            float cum = 0.f;
+            choice = n - 1;
+            for (int a = 0; a < n; ++a) {
+                cum += __expf((cv[a] - mx) / temp);
+                if (u < cum) { choice = a; break; }
+            }
+        }
+        out[blockIdx.x] = ci[choice];
+    }
+}
+
+int sample(const float* logits, int R, int V, int ld, int top_k, float top_p, float min_p, float temp, uint32_t seed,
+           const int* step_ctr, int* out, cudaStream_t s) {
+    DLP_REQUIRE(R > 0 && V > 0, "sample: bad shape");
+    if (temp <= 0.f) return argmax(logits, R, V, ld, out, s);
+    sample_kernel<<<R, 1024, 0, s>>>(logits, V, ld, top_k, top_p, min_p, temp, seed, step_ctr, out);
+    DLP_LAUNCH_CHECK();
+    return 0;
+}
+
+// cast helpers -------------------------------------------------------------------------------
+__global__ void f32_to_f16_kernel(const float* __restrict__ in, __half* __restrict__ out, size_t n) {
+    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) out[i] = __float2half_rn(in[i]);
+}
+int f32_to_f16(const float* in, __half* out, size_t n, cudaStream_t s) {
+    f32_to_f16_kernel<<<(unsigned)((n + 255) / 256), 256, 0, s>>>(in, out, n);
+    DLP_LAUNCH_CHECK();
+    return 0;
+}
+
+}  // namespace dlp

@@ -1,0 +1,290 @@
+// tcgen05 / TMEM / TMA GEMM for sm_100a:   Y[T, N] (op)= X[T, K] . W[N, K]^T
+//
+// Role in the engine: every prefill / batched-decode linear layer (QKV, attn-out, gate/up, down, lm_head).
+// The reference runs these through cuBLAS GemmEx or its mma.sync MMQ kernels
+// (llama.cpp/ggml/src/ggml-cuda/ggml-cuda.cu:1227-1371, mmq.cuh:3459); this is the Blackwell-native
+// replacement: weights are the UMMA "A" operand (M = 128 output features per CTA), tokens are the "B"
+// operand (N = BT tokens, 16..256), so small decode batches still fill the 128-lane datapath
+// ("swap-AB"), accumulators live in TMEM and the epilogue (fp16/fp32 store, fp32 residual
+// accumulate / split-K reduction, SwiGLU over a gate+up accumulator pair) reads them back with
+// tcgen05.ld.  Operands arrive through TMA with the 128-byte swizzle; a 3..8 stage mbarrier ring
+// decouples the TMA warp from the single MMA-issuing thread.
+#include "kernels.cuh"
+
+namespace dlp {
+
+constexpr int GEMM_BM = 128;  // output features per CTA (UMMA M)
+constexpr int GEMM_BK = 64;   // K elements per pipeline stage (= 128 B of fp16: one swizzle atom)
+
+enum GemmEpilogue : int { EPI_STORE_F16 = 0, EPI_STORE_F32 = 1, EPI_ATOMIC_ADD_F32 = 2, EPI_SWIGLU_F16 = 3,
+                          EPI_STORE_BF16 = 4 };
+
+struct GemmParams {
+    void* y;       // output [T, ldy]
+    int T, N, K;   // tokens, output features, reduction
+    int ldy;       // row stride of y in elements
+    int epilogue;
+    int k_blocks_per_split;
+};
+
+template <int BT, int NA>
+struct GemmCfg {
+    static constexpr int A_BYTES = GEMM_BM * GEMM_BK * 2;
+    static constexpr int B_BYTES = BT * GEMM_BK * 2;
+    static constexpr int STAGE_BYTES = NA * A_BYTES + B_BYTES;
+    static constexpr int STAGES_RAW = (200 * 1024) / STAGE_BYTES;
+    static constexpr int STAGES = STAGES_RAW > 8 ? 8 : STAGES_RAW;
+    static constexpr int TMEM_COLS_RAW = NA * BT;
+    static constexpr int TMEM_COLS = TMEM_COLS_RAW <= 32 ? 32 : TMEM_COLS_RAW <= 64 ? 64 : TMEM_COLS_RAW <= 128 ? 128
+                                     : TMEM_COLS_RAW <= 256 ? 256 : 512;
+    static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 /*align slack*/ + 256 /*barriers*/;
+};
+
+__device__ __forceinline__ float silu_f(float x) { return x / (1.f + __expf(-x)); }
+
+template <int BT, int NA, int AB_FMT>
+__global__ void __launch_bounds__(192, 1)
+gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tm_w0, const __grid_constant__ CUtensorMap tm_w1,
+                    const __grid_constant__ CUtensorMap tm_x, const GemmParams p) {
+    using Cfg = GemmCfg<BT, NA>;
+    constexpr int STAGES = Cfg::STAGES;
+    extern __shared__ uint8_t smem_raw[];
+    // 1024-byte alignment is required by the 128B swizzle atoms
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+    uint8_t* smem_a0 = smem;
+    uint8_t* smem_a1 = smem + STAGES * Cfg::A_BYTES;  // only when NA == 2
+    uint8_t* smem_b = smem + NA * STAGES * Cfg::A_BYTES;
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + STAGES * Cfg::STAGE_BYTES);
+    uint64_t* full_bar = bars;
+    uint64_t* empty_bar = bars + STAGES;
+    uint64_t* tmem_full_bar = bars + 2 * STAGES;
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * STAGES + 1);
+
+    const int warp = threadIdx.x >> 5;
+    const int lane = threadIdx.x & 31;
+    const int n0 = blockIdx.x * GEMM_BM;
+    const int t0 = blockIdx.y * BT;
+    const int total_kb = p.K / GEMM_BK;
+    const int kb_begin = blockIdx.z * p.k_blocks_per_split;
+    const int kb_end = min(total_kb, kb_begin + p.k_blocks_per_split);
+    const int num_kb = kb_end - kb_begin;
+
+    if (warp == 0 && lane == 0) {
+        tma_prefetch_desc(&tm_w0);
+        if (NA == 2) tma_prefetch_desc(&tm_w1);
+        tma_prefetch_desc(&tm_x);
+        for (int s = 0; s < STAGES; ++s) {
+            mbar_init(&full_bar[s], 1);
+            mbar_init(&empty_bar[s], 1);
+        }
+        mbar_init(tmem_full_bar, 1);
+        mbar_fence_init();
+    }
+    if (warp == 1) {
+        tmem_alloc(tmem_slot, Cfg::TMEM_COLS);
+        tmem_relinquish();
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+
+    if (warp == 0) {
+        // ===== TMA producer =====
+        if (lane == 0) {
+            int stage = 0;
+            uint32_t phase = 0;
+            for (int kb = 0; kb < num_kb; ++kb) {
+                mbar_wait(&empty_bar[stage], phase ^ 1);
+                mbar_expect_tx(&full_bar[stage], Cfg::STAGE_BYTES);
+                const int kc = (kb_begin + kb) * GEMM_BK;
+                tma_load_2d(smem_a0 + stage * Cfg::A_BYTES, &tm_w0, &full_bar[stage], kc, n0);
+                if (NA == 2) tma_load_2d(smem_a1 + stage * Cfg::A_BYTES, &tm_w1, &full_bar[stage], kc, n0);
+                tma_load_2d(smem_b + stage * Cfg::B_BYTES, &tm_x, &full_bar[stage], kc, t0);
+                if (++stage == STAGES) { stage = 0; phase ^= 1; }
+            }
+        }
+    } else if (warp == 1) {
+        // ===== MMA issuer (one thread) =====
+        if (lane == 0) {
+            constexpr uint32_t idesc = make_idesc_f16(GEMM_BM, BT, AB_FMT);
+            int stage = 0;
+            uint32_t phase = 0;
+            for (int kb = 0; kb < num_kb; ++kb) {
+                mbar_wait(&full_bar[stage], phase);
+                tc_fence_after();
+                const uint64_t da0 = make_smem_desc_sw128(smem_u32(smem_a0 + stage * Cfg::A_BYTES));
+                const uint64_t da1 = make_smem_desc_sw128(smem_u32(smem_a1 + stage * Cfg::A_BYTES));
+                const uint64_t db = make_smem_desc_sw128(smem_u32(smem_b + stage * Cfg::B_BYTES));
+#pragma unroll
+                for (int k = 0; k < GEMM_BK / 16; ++k) {
+                    const uint32_t acc = (kb > 0 || k > 0) ? 1u : 0u;
+                    // +32 bytes (>>4 = 2) per 16-element K step inside the swizzle atom
+                    tc_mma_f16(tmem_base, da0 + (uint64_t)(2 * k), db + (uint64_t)(2 * k), idesc, acc);
+                    if (NA == 2) tc_mma_f16(tmem_base + BT, da1 + (uint64_t)(2 * k), db + (uint64_t)(2 * k), idesc, acc);
+                }
+                tc_commit(&empty_bar[stage]);  // frees this smem slot once the MMAs above have read it
+                if (++stage == STAGES) { stage = 0; phase ^= 1; }
+            }
+            tc_commit(tmem_full_bar);  // accumulator complete
+        }
+    } else {
+        // ===== epilogue: 4 warps, warp%4 selects the TMEM lane quarter =====
+        const int q = warp & 3;
+        const int n = n0 + q * 32 + lane;
+        if (num_kb > 0) {
+            mbar_wait(tmem_full_bar, 0);
+            tc_fence_after();
+        }
+        const uint32_t lane_addr = tmem_base + ((uint32_t)(q * 32) << 16);
+        constexpr int CH = BT >= 32 ? 32 : 16;
+#pragma unroll 1
+        for (int c = 0; c < BT / CH; ++c) {
+            if (t0 + c * CH >= p.T) break;  // warp-uniform
+            uint32_t r0[CH], r1[CH];
+            if (num_kb > 0) {
+                if constexpr (CH == 32) {
+                    tmem_ld_32x32(lane_addr + c * CH, r0);
+                    if (NA == 2) tmem_ld_32x32(lane_addr + BT + c * CH, r1);
+                } else {
+                    tmem_ld_32x16(lane_addr + c * CH, r0);
+                    if (NA == 2) tmem_ld_32x16(lane_addr + BT + c * CH, r1);
+                }
+                tc_wait_ld();
+            } else {
+#pragma unroll
+                for (int j = 0; j < CH; ++j) { r0[j] = 0; r1[j] = 0; }
+            }
+            if (n < p.N) {
+#pragma unroll
+                for (int j = 0; j < CH; ++j) {
+                    const int t = t0 + c * CH + j;
+                    if (t < p.T) {
+                        const float v = __uint_as_float(r0[j]);
+                        const size_t o = (size_t)t * p.ldy + n;
+                        switch (p.epilogue) {
+                            case EPI_STORE_F16: reinterpret_cast<__half*>(p.y)[o] = __float2half_rn(v); break;
+                            case EPI_STORE_BF16: reinterpret_cast<__nv_bfloat16*>(p.y)[o] = __float2bfloat16_rn(v); break;
+                            case EPI_STORE_F32: reinterpret_cast<float*>(p.y)[o] = v; break;
+                            case EPI_ATOMIC_ADD_F32: atomicAdd(reinterpret_cast<float*>(p.y) + o, v); break;
+                            case EPI_SWIGLU_F16:
+                                if (NA == 2)
+                                    reinterpret_cast<__half*>(p.y)[o] = __float2half_rn(silu_f(v) * __uint_as_float(r1[j]));
+                                break;
+                        }
+                    }
+                }
+            }
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 1) {
+        tc_fence_after();
+        tmem_dealloc(tmem_base, Cfg::TMEM_COLS);
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
+// host side
+
+typedef CUresult (*PFN_encodeTiled)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                    const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                    CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static PFN_encodeTiled get_encode_fn() {
+    static PFN_encodeTiled fn = nullptr;
+    if (!fn) {
+        void* p = nullptr;
+        cudaDriverEntryPointQueryResult qres;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &qres) == cudaSuccess &&
+            qres == cudaDriverEntryPointSuccess)
+            fn = reinterpret_cast<PFN_encodeTiled>(p);
+    }
+    return fn;
+}
+
+// 2-D K-major tensor map: dims {K, rows}, row stride ld elements, box {64, box_rows}, 128B swizzle.
+int make_tmap_2d(CUtensorMap* out, const void* base, int is_bf16, uint64_t rows, uint64_t K, uint64_t ld, uint32_t box_rows) {
+    PFN_encodeTiled enc = get_encode_fn();
+    DLP_REQUIRE(enc != nullptr, "cuTensorMapEncodeTiled entry point unavailable (no CUDA driver?)");
+    DLP_REQUIRE((reinterpret_cast<uintptr_t>(base) & 15) == 0, "TMA base pointer must be 16-byte aligned");
+    DLP_REQUIRE((ld * 2) % 16 == 0, "TMA row stride must be a multiple of 16 bytes (ld=%llu)", (unsigned long long)ld);
+    cuuint64_t dims[2] = {K, rows};
+    cuuint64_t strides[1] = {ld * 2};
+    cuuint32_t box[2] = {GEMM_BK, box_rows};
+    cuuint32_t estr[2] = {1, 1};
+    CUresult r = enc(out, is_bf16 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2,
+                     const_cast<void*>(base), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                     CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    DLP_REQUIRE(r == CUDA_SUCCESS, "cuTensorMapEncodeTiled failed with CUresult %d", (int)r);
+    return 0;
+}
+
+template <int BT, int NA, int AB_FMT>
+static int launch_gemm(const CUtensorMap& tw0, const CUtensorMap& tw1, const CUtensorMap& tx, const GemmParams& p,
+                       int splits, cudaStream_t stream) {
+    using Cfg = GemmCfg<BT, NA>;
+    auto kern = gemm_tcgen05_kernel<BT, NA, AB_FMT>;
+    static bool configured = false;
+    if (!configured) {
+        DLP_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES));
+        configured = true;
+    }
+    dim3 grid((p.N + GEMM_BM - 1) / GEMM_BM, (p.T + BT - 1) / BT, splits);
+    kern<<<grid, 192, Cfg::SMEM_BYTES, stream>>>(tw0, tw1, tx, p);
+    DLP_LAUNCH_CHECK();
+    return 0;
+}
+
+// Y[T,N] (op)= X[T,K] . W0[N,K]^T  (and W1 for SwiGLU).  X/W are fp16 (is_bf16=0) or bf16 (is_bf16=1).
+int gemm_f16(const void* w0, const void* w1, int ldw, const void* x, int ldx, void* y, int ldy, int T, int N, int K,
+             int epilogue, int is_bf16, int split_k, cudaStream_t stream) {
+    DLP_REQUIRE(T > 0 && N > 0 && K > 0, "gemm: empty problem T=%d N=%d K=%d", T, N, K);
+    DLP_REQUIRE(K % GEMM_BK == 0, "gemm: K=%d must be a multiple of %d", K, GEMM_BK);
+    const int na = (epilogue == EPI_SWIGLU_F16) ? 2 : 1;
+    DLP_REQUIRE(na == 1 || w1 != nullptr, "gemm: SwiGLU epilogue needs the up-projection weight");
+    const int total_kb = K / GEMM_BK;
+    int splits = split_k;
+    if (splits <= 0) {  // auto: fill the machine when the epilogue can reduce across CTAs
+        splits = 1;
+        if (epilogue == EPI_ATOMIC_ADD_F32) {
+            const int bt_guess = T <= 16 ? 16 : T <= 32 ? 32 : T <= 64 ? 64 : T <= 128 ? 128 : 256;
+            const long tiles = (long)((N + GEMM_BM - 1) / GEMM_BM) * ((T + bt_guess - 1) / bt_guess);
+            const int sms = sm_count();
+            while (tiles * splits * 2 <= sms && total_kb / (splits * 2) >= 8) splits *= 2;
+        }
+    }
+    DLP_REQUIRE(splits == 1 || epilogue == EPI_ATOMIC_ADD_F32, "gemm: split-K needs the atomic-add epilogue");
+    if (splits > total_kb) splits = total_kb;
+    GemmParams p;
+    p.y = y; p.T = T; p.N = N; p.K = K; p.ldy = ldy; p.epilogue = epilogue;
+    p.k_blocks_per_split = (total_kb + splits - 1) / splits;
+    splits = (total_kb + p.k_blocks_per_split - 1) / p.k_blocks_per_split;
+
+    const int bt = T <= 16 ? 16 : T <= 32 ? 32 : T <= 64 ? 64 : T <= 128 ? 128 : 256;
+    CUtensorMap tw0, tw1, tx;
+    int rc;
+    if ((rc = make_tmap_2d(&tw0, w0, is_bf16, N, K, ldw, GEMM_BM))) return rc;
+    tw1 = tw0;
+    if (na == 2 && (rc = make_tmap_2d(&tw1, w1, is_bf16, N, K, ldw, GEMM_BM))) return rc;
+    if ((rc = make_tmap_2d(&tx, x, is_bf16, T, K, ldx, bt))) return rc;
+
+#define DLP_GEMM_CASE(BT_)                                                                         \
+    case BT_:                                                                                      \
+        if (na == 2) return is_bf16 ? launch_gemm<BT_, 2, 1>(tw0, tw1, tx, p, splits, stream)      \
+                                    : launch_gemm<BT_, 2, 0>(tw0, tw1, tx, p, splits, stream);     \
+        return is_bf16 ? launch_gemm<BT_, 1, 1>(tw0, tw1, tx, p, splits, stream)                   \
+                       : launch_gemm<BT_, 1, 0>(tw0, tw1, tx, p, splits, stream);
+    switch (bt) {
+        DLP_GEMM_CASE(16)
+        DLP_GEMM_CASE(32)
+        DLP_GEMM_CASE(64)
+        DLP_GEMM_CASE(128)
+        DLP_GEMM_CASE(256)
+    }
+#undef DLP_GEMM_CASE
+    return -1;
+}
+
+}  // namespace dlp

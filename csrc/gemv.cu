@@ -1,0 +1,273 @@
+// Bandwidth-bound decode linear layers:  y[T, N] (op)= x[T, K] . W[N, K]^T   for T in {1, 2, 4}
+//
+// Role: single-stream / tiny-batch decode, where every weight byte is read exactly once per token and
+// HBM bandwidth is the roofline.  Reference counterparts: `mul_mat_vec_f` (llama.cpp/ggml/src/ggml-cuda/
+// mmvf.cu) and `mul_mat_vec_q` (mmvq.cu:143) incl. their gate+up+GLU fusion (mmvq.cu:181-189,297-330).
+// Differences by design: activations stay fp16/fp32 (no q8_1 activation quantise pass), RMSNorm is fused
+// into the prologue (each CTA normalises x once into shared memory), the residual add is fused into the
+// epilogue, and every lane keeps 8 x 16-byte weight loads in flight (two row streams x 4-deep unroll).
+#include "kernels.cuh"
+
+namespace dlp {
+
+__device__ __forceinline__ float gv_silu(float x) { return x / (1.f + __expf(-x)); }
+
+template <int NT>
+__device__ __forceinline__ void stage_x(const GemvParams& p, int K, __half* xs, float* red) {
+    // xs[t][k] <- fp16 activations (optionally RMS-normalised from the fp32 residual stream)
+    const int tid = threadIdx.x, nth = blockDim.x;
+    if (p.norm_w == nullptr) {
+        const uint4* src = reinterpret_cast<const uint4*>(p.x);
+        uint4* dst = reinterpret_cast<uint4*>(xs);
+        const int n16 = NT * K / 8;
+        for (int i = tid; i < n16; i += nth) dst[i] = src[i];
+        __syncthreads();
+        return;
+    }
+    const float* h = reinterpret_cast<const float*>(p.x);
+#pragma unroll
+    for (int t = 0; t < NT; ++t) {
+        float ss = 0.f;
+        for (int k = tid * 4; k < K; k += nth * 4) {
+            const float4 v = *reinterpret_cast<const float4*>(h + (size_t)t * K + k);
+            ss += v.x * v.x + v.y * v.y + v.z * v.z + v.w * v.w;
+        }
+        ss = block_sum(ss, red);
+        const float rs = rsqrtf(ss / (float)K + p.eps);
+        for (int k = tid * 4; k < K; k += nth * 4) {
+            const float4 v = *reinterpret_cast<const float4*>(h + (size_t)t * K + k);
+            const float4 g = *reinterpret_cast<const float4*>(p.norm_w + k);
+            __half2 a = __floats2half2_rn(v.x * rs * g.x, v.y * rs * g.y);
+            __half2 b = __floats2half2_rn(v.z * rs * g.z, v.w * rs * g.w);
+            uint2 o;
+            o.x = *reinterpret_cast<uint32_t*>(&a);
+            o.y = *reinterpret_cast<uint32_t*>(&b);
+            *reinterpret_cast<uint2*>(xs + (size_t)t * K + k) = o;
+        }
+    }
+    __syncthreads();
+}
+
+template <int NT>
+__device__ __forceinline__ void gv_write(const GemvParams& p, int row, float (&acc)[2][NT], bool dual, int lane) {
+    // acc[s][t] is warp-uniform after the reductions; lanes split the stores
+    if (dual) {
+        if (lane < NT) {
+            float g = 0.f, u = 0.f;
+#pragma unroll
+            for (int t = 0; t < NT; ++t) if (t == lane) { g = acc[0][t]; u = acc[1][t]; }
+            reinterpret_cast<__half*>(p.y)[(size_t)lane * p.ldy + row] = __float2half_rn(gv_silu(g) * u);
+        }
+        return;
+    }
+    if (lane < 2 * NT) {
+        const int s = lane & 1, t = lane >> 1;
+        float v = 0.f;
+#pragma unroll
+        for (int tt = 0; tt < NT; ++tt) if (tt == t) v = s ? acc[1][tt] : acc[0][tt];
+        const size_t o = (size_t)t * p.ldy + row + s;
+        if (row + s < p.w0.N) {
+            if (p.out_mode == GV_STORE_F16) reinterpret_cast<__half*>(p.y)[o] = __float2half_rn(v);
+            else if (p.out_mode == GV_STORE_F32) reinterpret_cast<float*>(p.y)[o] = v;
+            else reinterpret_cast<float*>(p.y)[o] += v;  // GV_ADD_F32: each output has exactly one writer
+        }
+    }
+}
+
+// ---- dense fp16 / bf16 weights -----------------------------------------------------------------
+template <int NT, bool BF16>
+__global__ void __launch_bounds__(256) gemv_dense_kernel(const GemvParams p) {
+    extern __shared__ __align__(16) uint8_t gv_smem[];
+    const int K = p.w0.K, N = p.w0.N;
+    __half* xs = reinterpret_cast<__half*>(gv_smem);
+    __shared__ float red[32];
+    stage_x<NT>(p, K, xs, red);
+
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const bool dual = p.out_mode == GV_SWIGLU_F16;
+    const int rows_per_it = dual ? 1 : 2;
+    const int gw = blockIdx.x * 8 + warp, nw = gridDim.x * 8;
+    constexpr int U = 4;
+    for (int row = gw * rows_per_it; row < N; row += nw * rows_per_it) {
+        const uint8_t* wp[2];
+        wp[0] = p.w0.base + (size_t)row * K * 2;
+        wp[1] = dual ? p.w1.base + (size_t)row * K * 2 : p.w0.base + (size_t)min(row + 1, N - 1) * K * 2;
+        float acc[2][NT];
+#pragma unroll
+        for (int s = 0; s < 2; ++s)
+#pragma unroll
+            for (int t = 0; t < NT; ++t) acc[s][t] = 0.f;
+        for (int k = lane * 8; k < K; k += 256 * U) {
+            uint4 w[2][U];
+#pragma unroll
+            for (int u = 0; u < U; ++u)
+#pragma unroll
+                for (int s = 0; s < 2; ++s)
+                    w[s][u] = (k + u * 256 < K) ? ldg_nc_v4(wp[s] + (size_t)(k + u * 256) * 2) : make_uint4(0, 0, 0, 0);
+#pragma unroll
+            for (int u = 0; u < U; ++u) {
+                if (k + u * 256 < K) {
+                    float2 wf[2][4];
+#pragma unroll
+                    for (int s = 0; s < 2; ++s) {
+                        const uint32_t ww[4] = {w[s][u].x, w[s][u].y, w[s][u].z, w[s][u].w};
+#pragma unroll
+                        for (int i = 0; i < 4; ++i) wf[s][i] = BF16 ? bf2_to_f2(ww[i]) : h2_to_f2(ww[i]);
+                    }
+#pragma unroll
+                    for (int t = 0; t < NT; ++t) {
+                        const uint4 xv = *reinterpret_cast<const uint4*>(xs + (size_t)t * K + k + u * 256);
+                        const uint32_t xw[4] = {xv.x, xv.y, xv.z, xv.w};
+#pragma unroll
+                        for (int i = 0; i < 4; ++i) {
+                            const float2 xf = h2_to_f2(xw[i]);
+#pragma unroll
+                            for (int s = 0; s < 2; ++s) {
+                                acc[s][t] = fmaf(wf[s][i].x, xf.x, acc[s][t]);
+                                acc[s][t] = fmaf(wf[s][i].y, xf.y, acc[s][t]);
+                            }
+                        }
+                    }
+                }
+            }
+        }
+#pragma unroll
+        for (int s = 0; s < 2; ++s)
+#pragma unroll
+            for (int t = 0; t < NT; ++t) acc[s][t] = warp_sum(acc[s][t]);
+        gv_write<NT>(p, row, acc, dual, lane);
+    }
+}
+
+// ---- block-quantised weights ---------------------------------------------------------------------
+template <int WT, int NT>
+__global__ void __launch_bounds__(256) gemv_quant_kernel(const GemvParams p) {
+    extern __shared__ __align__(16) uint8_t gv_smem[];
+    const int K = p.w0.K, N = p.w0.N;
+    __half* xs = reinterpret_cast<__half*>(gv_smem);
+    float* xsum = reinterpret_cast<float*>(gv_smem + (size_t)NT * K * 2);  // [NT][K/16] sums of x per 16 elements
+    __shared__ float red[32];
+    stage_x<NT>(p, K, xs, red);
+    constexpr bool HAS_BIAS = (WT == W_Q4_K || WT == W_Q5_K);
+    if (HAS_BIAS) {
+        for (int i = threadIdx.x; i < NT * (K / 16); i += blockDim.x) {
+            const __half2* xp = reinterpret_cast<const __half2*>(xs + (size_t)i * 16);
+            float s = 0.f;
+#pragma unroll
+            for (int j = 0; j < 8; ++j) { const float2 f = __half22float2(xp[j]); s += f.x + f.y; }
+            xsum[i] = s;
+        }
+        __syncthreads();
+    }
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const bool dual = p.out_mode == GV_SWIGLU_F16;
+    const int rows_per_it = dual ? 1 : 2;
+    const int gw = blockIdx.x * 8 + warp, nw = gridDim.x * 8;
+    const int nchunk = K / 32;
+    for (int row = gw * rows_per_it; row < N; row += nw * rows_per_it) {
+        float acc[2][NT];
+#pragma unroll
+        for (int s = 0; s < 2; ++s)
+#pragma unroll
+            for (int t = 0; t < NT; ++t) acc[s][t] = 0.f;
+        const int row1 = dual ? row : min(row + 1, N - 1);
+#pragma unroll 2
+        for (int c = lane; c < nchunk; c += 32) {
+            QChunk ch[2];
+            load_chunk<WT>(p.w0, row, c, ch[0]);
+            load_chunk<WT>(dual ? p.w1 : p.w0, row1, c, ch[1]);
+#pragma unroll
+            for (int g = 0; g < 2; ++g) {
+                const int kk = ch[0].k[g];  // identical for both streams (same chunk index)
+#pragma unroll
+                for (int t = 0; t < NT; ++t) {
+                    const uint4 xa = *reinterpret_cast<const uint4*>(xs + (size_t)t * K + kk);
+                    const uint4 xb = *reinterpret_cast<const uint4*>(xs + (size_t)t * K + kk + 8);
+                    const uint32_t xw[8] = {xa.x, xa.y, xa.z, xa.w, xb.x, xb.y, xb.z, xb.w};
+                    float d0 = 0.f, d1 = 0.f;
+#pragma unroll
+                    for (int i = 0; i < 8; ++i) {
+                        const float2 xf = h2_to_f2(xw[i]);
+                        const float2 q0 = __half22float2(ch[0].q[g][i]);
+                        const float2 q1 = __half22float2(ch[1].q[g][i]);
+                        d0 = fmaf(q0.x, xf.x, d0); d0 = fmaf(q0.y, xf.y, d0);
+                        d1 = fmaf(q1.x, xf.x, d1); d1 = fmaf(q1.y, xf.y, d1);
+                    }
+                    acc[0][t] = fmaf(ch[0].scale[g], d0, acc[0][t]);
+                    acc[1][t] = fmaf(ch[1].scale[g], d1, acc[1][t]);
+                    if (HAS_BIAS) {
+                        const float sx = xsum[t * (K / 16) + (kk >> 4)];
+                        acc[0][t] = fmaf(ch[0].bias[g], sx, acc[0][t]);
+                        acc[1][t] = fmaf(ch[1].bias[g], sx, acc[1][t]);
+                    }
+                }
+            }
+        }
+#pragma unroll
+        for (int s = 0; s < 2; ++s)
+#pragma unroll
+            for (int t = 0; t < NT; ++t) acc[s][t] = warp_sum(acc[s][t]);
+        gv_write<NT>(p, row, acc, dual, lane);
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
+template <typename Kern>
+static int launch_gemv(Kern kern, const GemvParams& p, size_t smem, cudaStream_t stream) {
+    static thread_local const void* configured[64];
+    static thread_local int n_configured = 0;
+    bool seen = false;
+    for (int i = 0; i < n_configured; ++i) seen |= configured[i] == (const void*)kern;
+    if (!seen) {
+        DLP_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+        if (n_configured < 64) configured[n_configured++] = (const void*)kern;
+    }
+    const bool dual = p.out_mode == GV_SWIGLU_F16;
+    const int rows_per_block = 8 * (dual ? 1 : 2);
+    int blocks = (p.w0.N + rows_per_block - 1) / rows_per_block;
+    const int max_blocks = sm_count() * 4;
+    if (blocks > max_blocks) blocks = max_blocks;
+    kern<<<blocks, 256, smem, stream>>>(p);
+    DLP_LAUNCH_CHECK();
+    return 0;
+}
+
+int gemv(const GemvParams& p, int wtype, cudaStream_t stream) {
+    const int K = p.w0.K, N = p.w0.N, T = p.T;
+    DLP_REQUIRE(T == 1 || T == 2 || T == 4, "gemv: T=%d unsupported (1, 2 or 4; use the tcgen05 GEMM above that)", T);
+    DLP_REQUIRE(K % 256 == 0, "gemv: K=%d must be a multiple of 256", K);
+    DLP_REQUIRE(N % 2 == 0, "gemv: N=%d must be even", N);
+    DLP_REQUIRE(p.out_mode != GV_SWIGLU_F16 || p.w1.base != nullptr, "gemv: SwiGLU needs both gate and up weights");
+    size_t smem = (size_t)T * K * 2;
+    const bool quant_bias = (wtype == W_Q4_K || wtype == W_Q5_K);
+    if (quant_bias) smem += (size_t)T * (K / 16) * 4;
+    DLP_REQUIRE(smem <= 200 * 1024, "gemv: activations (%zu B) do not fit in shared memory", smem);
+#define DLP_GV_T(KERN, ...)                                                            \
+    switch (T) {                                                                       \
+        case 1: return launch_gemv(KERN<__VA_ARGS__ 1>, p, smem, stream);              \
+        case 2: return launch_gemv(KERN<__VA_ARGS__ 2>, p, smem, stream);              \
+        default: return launch_gemv(KERN<__VA_ARGS__ 4>, p, smem, stream);             \
+    }
+    switch (wtype) {
+        case W_F16:
+            switch (T) {
+                case 1: return launch_gemv(gemv_dense_kernel<1, false>, p, smem, stream);
+                case 2: return launch_gemv(gemv_dense_kernel<2, false>, p, smem, stream);
+                default: return launch_gemv(gemv_dense_kernel<4, false>, p, smem, stream);
+            }
+        case W_BF16:
+            switch (T) {
+                case 1: return launch_gemv(gemv_dense_kernel<1, true>, p, smem, stream);
+                case 2: return launch_gemv(gemv_dense_kernel<2, true>, p, smem, stream);
+                default: return launch_gemv(gemv_dense_kernel<4, true>, p, smem, stream);
+            }
+        case W_Q8_0: DLP_GV_T(gemv_quant_kernel, W_Q8_0, )
+        case W_Q4_K: DLP_GV_T(gemv_quant_kernel, W_Q4_K, )
+        case W_Q5_K: DLP_GV_T(gemv_quant_kernel, W_Q5_K, )
+        case W_Q6_K: DLP_GV_T(gemv_quant_kernel, W_Q6_K, )
+    }
+#undef DLP_GV_T
+    DLP_REQUIRE(false, "gemv: unsupported weight type %d", wtype);
+}
+
+}  // namespace dlp

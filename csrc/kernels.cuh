@@ -1,0 +1,52 @@
+// Internal kernel-launcher interface shared by the .cu translation units of libdlp_b200.so.
+#pragma once
+#include "quant.cuh"
+
+namespace dlp {
+
+enum GemvOut : int { GV_STORE_F16 = 0, GV_STORE_F32 = 1, GV_ADD_F32 = 2, GV_SWIGLU_F16 = 3 };
+
+struct GemvParams {
+    QWeight w0, w1;       // w1 only for the SwiGLU (gate, up) pair
+    const void* x;        // fp16 [T, K]  or, with norm fusion, fp32 h [T, K]
+    const float* norm_w;  // non-null => x is fp32 and RMSNorm(x) * norm_w is applied in the prologue
+    float eps;
+    void* y;
+    int ldy;
+    int out_mode;
+    int T;
+};
+
+struct AttnParams {
+    const __half* q;        // [nq, Hq, D]  (already scaled by 1/sqrt(D) and rotated)
+    const __half* kc;       // [n_pages][Hkv][page][D]
+    const __half* vc;
+    const int* block_table; // [n_rows, max_pages]
+    const int* bt_row;      // [nq] block-table row of each query (nullptr => row = query index)
+    const int* kv_len;      // [nq] number of keys visible to each query
+    __half* out;            // [nq, Hq, D]
+    float* part_o;          // [nq, Hq, n_splits, D]   (n_splits > 1)
+    float* part_ml;         // [nq, Hq, n_splits, 2]
+    int nq, Hq, Hkv, max_pages, page_size, n_splits;
+};
+
+int gemv(const GemvParams& p, int wtype, cudaStream_t stream);
+int gemm_f16(const void* w0, const void* w1, int ldw, const void* x, int ldx, void* y, int ldy, int T, int N, int K,
+             int epilogue, int is_bf16, int split_k, cudaStream_t stream);
+int dequant_rows_f32(const QWeight& w, int wtype, const int* row_ids, int n_rows, float* out, int ld_out, cudaStream_t s);
+int dequant_rows_f16(const QWeight& w, int wtype, const int* row_ids, int n_rows, __half* out, int ld_out, cudaStream_t s);
+int rmsnorm(float* h, const float* delta, const float* w, __half* out, int T, int E, float eps, cudaStream_t s);
+int rope_kv(const void* qkv, int qkv_is_f16, const int* pos, const int* slot, const float* inv_freq, __half* q_out,
+            __half* kc, __half* vc, int T, int Hq, int Hkv, int D, int n_rot, int page_size, int neox, float q_scale,
+            cudaStream_t s);
+int swiglu(const void* gu, int is_f16, __half* out, int T, int F, int ld_in, cudaStream_t s);
+int advance(int* seq_len, int* pos, int* slot, const int* block_table, int max_pages, int page_size, int n, cudaStream_t s);
+int argmax(const float* logits, int R, int V, int ld, int* out, cudaStream_t s);
+int sample(const float* logits, int R, int V, int ld, int top_k, float top_p, float min_p, float temp, uint32_t seed,
+           const int* step_ctr, int* out, cudaStream_t s);
+int f32_to_f16(const float* in, __half* out, size_t n, cudaStream_t s);
+int attn_paged(const AttnParams& p, int D, cudaStream_t s);
+int attn_prefill(const __half* q, const __half* kc, const __half* vc, const int* bt_row, __half* out, int T, int pos0,
+                 int Hq, int Hkv, int D, int page_size, cudaStream_t s);
+
+}  // namespace dlp

@@ -1,0 +1,367 @@
+"""Block-quant codecs (numpy, vectorised) for the GGUF tensor types this engine serves.
+
+These are the *host-side oracles* for every dequant-fused CUDA kernel in `csrc/` and the codecs used
+by the synthetic-model writer.  The bit layouts are the on-disk contract described by the reference's
+block structs (`llama.cpp/ggml/src/ggml-common.h:170-336`); the decode formulas correspond to
+`dequantize_row_q8_0` / `get_scale_min_k4` / `dequantize_row_q4_K` / `dequantize_row_q6_K`
+(`llama.cpp/ggml/src/ggml-quants.c:401,703,1352,1762`).  The encoders here are our own (closed-form
+min/max fits, not the reference's iterative search): any valid block decodes identically everywhere,
+which is all the file format requires.
+
+All functions operate on flat `uint8` byte buffers <-> `float32` arrays whose last dimension is a
+multiple of the block size.
+"""
+from __future__ import annotations
+
+import numpy as np
+
+from .constants import BLOCK_GEOMETRY, GGMLType, QK_K
+
+# --------------------------------------------------------------------------------------------
+# helpers
+
+
+def _blocks(raw: np.ndarray, ggml_type: GGMLType) -> np.ndarray:
+    per, nbytes = BLOCK_GEOMETRY[ggml_type]
+    raw = np.ascontiguousarray(raw).view(np.uint8).reshape(-1)
+    if raw.size % nbytes:
+        raise ValueError(f"byte length {raw.size} is not a multiple of {nbytes} for {ggml_type!r}")
+    return raw.reshape(-1, nbytes)
+
+
+def _f16(col: np.ndarray) -> np.ndarray:
+    """Interpret a [..., 2] uint8 column pair as little-endian fp16 -> float32 [...]."""
+    return np.ascontiguousarray(col).view("<f2").astype(np.float32)[..., 0]
+
+
+def bf16_to_f32(u16: np.ndarray) -> np.ndarray:
+    return (u16.astype(np.uint32) << 16).view(np.float32)
+
+
+def f32_to_bf16(x: np.ndarray) -> np.ndarray:
+    """Round-to-nearest-even fp32 -> bf16 bit pattern (uint16)."""
+    u = np.ascontiguousarray(x, dtype=np.float32).view(np.uint32)
+    rounded = u + (0x7FFF + ((u >> 16) & 1))
+    out = (rounded >> 16).astype(np.uint16)
+    nan = np.isnan(x)
+    if nan.any():
+        out = np.where(nan, np.uint16(0x7FC0), out)
+    return out
+
+
+# --------------------------------------------------------------------------------------------
+# K-quant 6-bit scale/min packing (12 bytes hold 8 scales + 8 mins)
+
+
+def unpack_scale_min_k4(scales: np.ndarray) -> tuple[np.ndarray, np.ndarray]:
+    """scales: [nb, 12] uint8 -> (sc [nb, 8], mn [nb, 8]) uint8 in 0..63."""
+    s = scales.astype(np.uint8)
+    sc = np.empty(s.shape[:-1] + (8,), np.uint8)
+    mn = np.empty_like(sc)
+    sc[..., :4] = s[..., 0:4] & 63
+    mn[..., :4] = s[..., 4:8] & 63
+    sc[..., 4:] = (s[..., 8:12] & 0x0F) | ((s[..., 0:4] >> 6) << 4)
+    mn[..., 4:] = (s[..., 8:12] >> 4) | ((s[..., 4:8] >> 6) << 4)
+    return sc, mn
+
+
+def pack_scale_min_k4(sc: np.ndarray, mn: np.ndarray) -> np.ndarray:
+    """Inverse of :func:`unpack_scale_min_k4` (inputs 0..63)."""
+    sc = sc.astype(np.uint8)
+    mn = mn.astype(np.uint8)
+    out = np.zeros(sc.shape[:-1] + (12,), np.uint8)
+    out[..., 0:4] = (sc[..., :4] & 63) | ((sc[..., 4:] >> 4) << 6)
+    out[..., 4:8] = (mn[..., :4] & 63) | ((mn[..., 4:] >> 4) << 6)
+    out[..., 8:12] = (sc[..., 4:] & 0x0F) | ((mn[..., 4:] & 0x0F) << 4)
+    return out
+
+
+# --------------------------------------------------------------------------------------------
+# dequantise
+
+
+def dequant_q8_0(raw: np.ndarray) -> np.ndarray:
+    b = _blocks(raw, GGMLType.Q8_0)
+    d = _f16(b[:, 0:2])
+    q = b[:, 2:].view(np.int8).astype(np.float32)
+    return (d[:, None] * q).reshape(-1)
+
+
+def dequant_q4_0(raw: np.ndarray) -> np.ndarray:
+    b = _blocks(raw, GGMLType.Q4_0)
+    d = _f16(b[:, 0:2])
+    qs = b[:, 2:]
+    lo = (qs & 0x0F).astype(np.int8) - 8
+    hi = (qs >> 4).astype(np.int8) - 8
+    q = np.concatenate([lo, hi], axis=1).astype(np.float32)
+    return (d[:, None] * q).reshape(-1)
+
+
+def dequant_q4_k(raw: np.ndarray) -> np.ndarray:
+    b = _blocks(raw, GGMLType.Q4_K)
+    d = _f16(b[:, 0:2])
+    dmin = _f16(b[:, 2:4])
+    sc, mn = unpack_scale_min_k4(b[:, 4:16])
+    qs = b[:, 16:144].reshape(-1, 4, 32)  # 4 chunks of 64 values, 32 bytes each
+    lo = (qs & 0x0F).astype(np.float32)  # sub-block 2j
+    hi = (qs >> 4).astype(np.float32)  # sub-block 2j+1
+    q = np.stack([lo, hi], axis=2).reshape(-1, 8, 32)
+    scale = d[:, None] * sc.astype(np.float32)
+    minv = dmin[:, None] * mn.astype(np.float32)
+    return (scale[:, :, None] * q - minv[:, :, None]).reshape(-1)
+
+
+def dequant_q5_k(raw: np.ndarray) -> np.ndarray:
+    b = _blocks(raw, GGMLType.Q5_K)
+    d = _f16(b[:, 0:2])
+    dmin = _f16(b[:, 2:4])
+    sc, mn = unpack_scale_min_k4(b[:, 4:16])
+    qh = b[:, 16:48]  # [nb, 32]
+    qs = b[:, 48:176].reshape(-1, 4, 32)
+    lo = (qs & 0x0F).astype(np.uint8)
+    hi = (qs >> 4).astype(np.uint8)
+    q4 = np.stack([lo, hi], axis=2).reshape(-1, 8, 32)
+    bits = ((qh[:, None, :] >> np.arange(8, dtype=np.uint8)[None, :, None]) & 1).astype(np.uint8)
+    q = (q4 + (bits << 4)).astype(np.float32)
+    scale = d[:, None] * sc.astype(np.float32)
+    minv = dmin[:, None] * mn.astype(np.float32)
+    return (scale[:, :, None] * q - minv[:, :, None]).reshape(-1)
+
+
+def dequant_q6_k(raw: np.ndarray) -> np.ndarray:
+    b = _blocks(raw, GGMLType.Q6_K)
+    ql = b[:, 0:128].reshape(-1, 2, 64)
+    qh = b[:, 128:192].reshape(-1, 2, 32)
+    sc = b[:, 192:208].view(np.int8).astype(np.float32).reshape(-1, 2, 8)
+    d = _f16(b[:, 208:210])
+    l0 = ql[:, :, :32]
+    l1 = ql[:, :, 32:]
+    q1 = (l0 & 0x0F) | (((qh >> 0) & 3) << 4)
+    q2 = (l1 & 0x0F) | (((qh >> 2) & 3) << 4)
+    q3 = (l0 >> 4) | (((qh >> 4) & 3) << 4)
+    q4 = (l1 >> 4) | (((qh >> 6) & 3) << 4)
+    q = np.stack([q1, q2, q3, q4], axis=2).astype(np.int16) - 32  # [nb, 2, 4, 32]
+    # scale index within a 128-half: is = l//16 + 2*k for quarter k
+    idx = (np.arange(32) // 16)[None, :] + 2 * np.arange(4)[:, None]  # [4, 32]
+    s = sc[:, :, idx]  # [nb, 2, 4, 32]
+    return (d[:, None, None, None] * s * q.astype(np.float32)).reshape(-1)
+
+
+def dequantize(raw: np.ndarray, ggml_type: GGMLType, shape: tuple[int, ...] | None = None) -> np.ndarray:
+    """Decode a raw byte buffer of `ggml_type` to float32 (optionally reshaped, row-major)."""
+    t = GGMLType(ggml_type)
+    raw = np.ascontiguousarray(raw).view(np.uint8).reshape(-1)
+    if t == GGMLType.F32:
+        out = raw.view("<f4").astype(np.float32)
+    elif t == GGMLType.F16:
+        out = raw.view("<f2").astype(np.float32)
+    elif t == GGMLType.BF16:
+        out = bf16_to_f32(raw.view("<u2"))
+    elif t == GGMLType.Q8_0:
+        out = dequant_q8_0(raw)
+    elif t == GGMLType.Q4_0:
+        out = dequant_q4_0(raw)
+    elif t == GGMLType.Q4_K:
+        out = dequant_q4_k(raw)
+    elif t == GGMLType.Q5_K:
+        out = dequant_q5_k(raw)
+    elif t == GGMLType.Q6_K:
+        out = dequant_q6_k(raw)
+    else:
+        raise NotImplementedError(f"dequantize: unsupported type {t!r}")
+    return out.reshape(shape) if shape is not None else out
+
+
+# --------------------------------------------------------------------------------------------
+# quantise
+
+
+def _nearest_int(x: np.ndarray) -> np.ndarray:
+    return np.rint(x).astype(np.int32)
+
+
+def quant_q8_0(x: np.ndarray) -> np.ndarray:
+    x = np.ascontiguousarray(x, dtype=np.float32).reshape(-1, 32)
+    amax = np.abs(x).max(axis=1)
+    d = (amax / 127.0).astype(np.float16)
+    df = d.astype(np.float32)
+    inv = np.where(df > 0, 1.0 / np.where(df > 0, df, 1.0), 0.0)
+    q = np.clip(_nearest_int(x * inv[:, None]), -127, 127).astype(np.int8)
+    out = np.empty((x.shape[0], 34), np.uint8)
+    out[:, 0:2] = d.view(np.uint8).reshape(-1, 2)
+    out[:, 2:] = q.view(np.uint8)
+    return out.reshape(-1)
+
+
+def quant_q4_0(x: np.ndarray) -> np.ndarray:
+    x = np.ascontiguousarray(x, dtype=np.float32).reshape(-1, 32)
+    idx = np.abs(x).argmax(axis=1)
+    mx = x[np.arange(x.shape[0]), idx]
+    d = (mx / -8.0).astype(np.float16)
+    df = d.astype(np.float32)
+    inv = np.where(df != 0, 1.0 / np.where(df != 0, df, 1.0), 0.0)
+    q = np.clip(_nearest_int(x * inv[:, None] + 8.0), 0, 15).astype(np.uint8)
+    out = np.empty((x.shape[0], 18), np.uint8)
+    out[:, 0:2] = d.view(np.uint8).reshape(-1, 2)
+    out[:, 2:] = q[:, :16] | (q[:, 16:] << 4)
+    return out.reshape(-1)
+
+
+def _kquant_affine_fit(x: np.ndarray, nmax: int):
+    """Per-sub-block affine fit  x ~= scale*q - minv  with q in [0, nmax], minv >= 0.
+
+    x: [nb, 8, 32].  Returns float scale/minv [nb, 8]."""
+    mn = np.minimum(x.min(axis=2), 0.0)
+    mx = x.max(axis=2)
+    scale = (mx - mn) / float(nmax)
+    return scale, -mn
+
+
+def _kquant_pack_super(scale: np.ndarray, minv: np.ndarray):
+    """6-bit quantise sub-block scales/mins against fp16 super-scales d / dmin."""
+    smax = scale.max(axis=1)
+    mmax = minv.max(axis=1)
+    d = (smax / 63.0).astype(np.float16)
+    dmin = (mmax / 63.0).astype(np.float16)
+    df = d.astype(np.float32)
+    dmf = dmin.astype(np.float32)
+    inv_d = np.where(df > 0, 1.0 / np.where(df > 0, df, 1.0), 0.0)
+    inv_m = np.where(dmf > 0, 1.0 / np.where(dmf > 0, dmf, 1.0), 0.0)
+    sc = np.clip(_nearest_int(scale * inv_d[:, None]), 0, 63).astype(np.uint8)
+    mq = np.clip(_nearest_int(minv * inv_m[:, None]), 0, 63).astype(np.uint8)
+    return d, dmin, sc, mq
+
+
+def quant_q4_k(x: np.ndarray) -> np.ndarray:
+    x = np.ascontiguousarray(x, dtype=np.float32).reshape(-1, 8, 32)
+    scale, minv = _kquant_affine_fit(x, 15)
+    d, dmin, sc, mq = _kquant_pack_super(scale, minv)
+    eff_s = d.astype(np.float32)[:, None] * sc
+    eff_m = dmin.astype(np.float32)[:, None] * mq
+    inv = np.where(eff_s > 0, 1.0 / np.where(eff_s > 0, eff_s, 1.0), 0.0)
+    q = np.clip(_nearest_int((x + eff_m[:, :, None]) * inv[:, :, None]), 0, 15).astype(np.uint8)
+    out = np.empty((x.shape[0], 144), np.uint8)
+    out[:, 0:2] = d.view(np.uint8).reshape(-1, 2)
+    out[:, 2:4] = dmin.view(np.uint8).reshape(-1, 2)
+    out[:, 4:16] = pack_scale_min_k4(sc, mq)
+    q = q.reshape(-1, 4, 2, 32)
+    out[:, 16:144] = (q[:, :, 0, :] | (q[:, :, 1, :] << 4)).reshape(-1, 128)
+    return out.reshape(-1)
+
+
+def quant_q5_k(x: np.ndarray) -> np.ndarray:
+    x = np.ascontiguousarray(x, dtype=np.float32).reshape(-1, 8, 32)
+    scale, minv = _kquant_affine_fit(x, 31)
+    d, dmin, sc, mq = _kquant_pack_super(scale, minv)
+    eff_s = d.astype(np.float32)[:, None] * sc
+    eff_m = dmin.astype(np.float32)[:, None] * mq
+    inv = np.where(eff_s > 0, 1.0 / np.where(eff_s > 0, eff_s, 1.0), 0.0)
+    q = np.clip(_nearest_int((x + eff_m[:, :, None]) * inv[:, :, None]), 0, 31).astype(np.uint8)
+    out = np.empty((x.shape[0], 176), np.uint8)
+    out[:, 0:2] = d.view(np.uint8).reshape(-1, 2)
+    out[:, 2:4] = dmin.view(np.uint8).reshape(-1, 2)
+    out[:, 4:16] = pack_scale_min_k4(sc, mq)
+    hb = (q >> 4) & 1  # [nb, 8, 32]
+    qh = np.zeros((x.shape[0], 32), np.uint8)
+    for j in range(8):
+        qh |= (hb[:, j, :] << j).astype(np.uint8)
+    out[:, 16:48] = qh
+    q4 = (q & 0x0F).reshape(-1, 4, 2, 32)
+    out[:, 48:176] = (q4[:, :, 0, :] | (q4[:, :, 1, :] << 4)).reshape(-1, 128)
+    return out.reshape(-1)
+
+
+def quant_q6_k(x: np.ndarray) -> np.ndarray:
+    x = np.ascontiguousarray(x, dtype=np.float32).reshape(-1, 16, 16)  # 16 sub-blocks of 16
+    amax = np.abs(x).max(axis=2)  # [nb, 16]
+    sub = amax / 31.0  # symmetric: q in [-31, 31]  (-32 never needed)
+    smax = sub.max(axis=1)
+    d = (smax / 127.0).astype(np.float16)
+    df = d.astype(np.float32)
+    inv_d = np.where(df > 0, 1.0 / np.where(df > 0, df, 1.0), 0.0)
+    sc = np.clip(_nearest_int(sub * inv_d[:, None]), 0, 127).astype(np.int8)
+    eff = df[:, None] * sc.astype(np.float32)
+    inv = np.where(eff > 0, 1.0 / np.where(eff > 0, eff, 1.0), 0.0)
+    q = (np.clip(_nearest_int(x * inv[:, :, None]), -32, 31) + 32).astype(np.uint8)  # 0..63
+    q = q.reshape(-1, 2, 4, 32)  # [nb, half, quarter k, l]; value index = half*128 + k*32 + l
+    lo = q & 0x0F
+    hi = q >> 4
+    ql = np.empty((x.shape[0], 2, 64), np.uint8)
+    ql[:, :, :32] = lo[:, :, 0, :] | (lo[:, :, 2, :] << 4)
+    ql[:, :, 32:] = lo[:, :, 1, :] | (lo[:, :, 3, :] << 4)
+    qh = hi[:, :, 0, :] | (hi[:, :, 1, :] << 2) | (hi[:, :, 2, :] << 4) | (hi[:, :, 3, :] << 6)
+    out = np.empty((x.shape[0], 210), np.uint8)
+    out[:, 0:128] = ql.reshape(-1, 128)
+    out[:, 128:192] = qh.reshape(-1, 64)
+    out[:, 192:208] = sc.view(np.uint8)
+    out[:, 208:210] = d.view(np.uint8).reshape(-1, 2)
+    return out.reshape(-1)
+
+
+def quantize(x: np.ndarray, ggml_type: GGMLType) -> np.ndarray:
+    """Encode float32 data (last dim multiple of block size) -> raw uint8 bytes."""
+    t = GGMLType(ggml_type)
+    x = np.ascontiguousarray(x, dtype=np.float32)
+    if t == GGMLType.F32:
+        return x.astype("<f4").view(np.uint8).reshape(-1)
+    if t == GGMLType.F16:
+        return x.astype("<f2").view(np.uint8).reshape(-1)
+    if t == GGMLType.BF16:
+        return f32_to_bf16(x).astype("<u2").view(np.uint8).reshape(-1)
+    per, _ = BLOCK_GEOMETRY[t]
+    if x.shape[-1] % per:
+        raise ValueError(f"last dim {x.shape[-1]} not a multiple of {per} for {t!r}")
+    fn = {
+        GGMLType.Q8_0: quant_q8_0,
+        GGMLType.Q4_0: quant_q4_0,
+        GGMLType.Q4_K: quant_q4_k,
+        GGMLType.Q5_K: quant_q5_k,
+        GGMLType.Q6_K: quant_q6_k,
+    }.get(t)
+    if fn is None:
+        raise NotImplementedError(f"quantize: unsupported type {t!r}")
+    return fn(x)
+
+
+# --------------------------------------------------------------------------------------------
+# direct random block synthesis (fast path for multi-GB synthetic checkpoints)
+
+
+def random_blocks(ggml_type: GGMLType, n_elements: int, rng: np.random.Generator, std: float = 0.02) -> np.ndarray:
+    """Produce *valid* random blocks of `ggml_type` whose decoded values have roughly N(0, std) spread,
+    without ever materialising float weights (used for 8B/70B-shape random-init checkpoints)."""
+    t = GGMLType(ggml_type)
+    per, nbytes = BLOCK_GEOMETRY[t]
+    if n_elements % per:
+        raise ValueError("element count must be a multiple of the block size")
+    nb = n_elements // per
+    if t in (GGMLType.F32, GGMLType.F16, GGMLType.BF16):
+        x = rng.standard_normal(n_elements, dtype=np.float32) * std
+        return quantize(x, t)
+    out = rng.integers(0, 256, size=(nb, nbytes), dtype=np.uint8)
+
+    def put_f16(col: int, val: np.ndarray):
+        out[:, col:col + 2] = val.astype(np.float16).view(np.uint8).reshape(-1, 2)
+
+    jitter = rng.uniform(0.75, 1.25, size=nb).astype(np.float32)
+    if t == GGMLType.Q8_0:
+        put_f16(0, jitter * (3.0 * std / 127.0))
+        # shape int8 payload ~ N(0, 42) so 3 sigma ~ 127
+        q = np.clip(np.rint(rng.standard_normal((nb, 32), dtype=np.float32) * 42.0), -127, 127).astype(np.int8)
+        out[:, 2:] = q.view(np.uint8)
+    elif t == GGMLType.Q4_0:
+        put_f16(0, jitter * (3.0 * std / 8.0))
+    elif t in (GGMLType.Q4_K, GGMLType.Q5_K):
+        nmax = 15 if t == GGMLType.Q4_K else 31
+        # value = d*sc*q - dmin*m ; centre around zero: dmin*m ~ d*sc*nmax/2
+        put_f16(0, jitter * (6.0 * std / nmax / 48.0))
+        put_f16(2, jitter * (3.0 * std / 48.0))
+        sc = rng.integers(32, 64, size=(nb, 8), dtype=np.uint8)
+        mn = rng.integers(40, 56, size=(nb, 8), dtype=np.uint8)
+        out[:, 4:16] = pack_scale_min_k4(sc, mn)
+    elif t == GGMLType.Q6_K:
+        out[:, 192:208] = rng.integers(32, 127, size=(nb, 16), dtype=np.int8).view(np.uint8)
+        put_f16(208, jitter * (3.0 * std / 32.0 / 96.0))
+    else:
+        raise NotImplementedError(f"random_blocks: unsupported type {t!r}")
+    return out.reshape(-1)

@@ -1,0 +1,209 @@
+"""Random-init GGUF checkpoint synthesis.
+
+Writes loadable llama/mixtral-architecture GGUF files in F16 / BF16 / Q8_0 / Q4_K_M with the tensor and
+KV names the reference expects (`llama.cpp/src/llama-arch.cpp:128-337`), so that the *same file* can be
+served by this engine and by the reference's `llama-bench` for A/B runs.  The Q4_K_M type mix follows
+the public recipe (`llama.cpp/src/llama-quant.cpp:302-405`): mostly Q4_K, `output.weight` Q6_K, and
+"more bits" (Q6_K) for attn_v / ffn_down in the first/last eighth and every third layer in between.
+
+Two payload modes:
+  * ``exact=True``  - draw float weights, then quantise (small models; oracle tests need real values);
+  * ``exact=False`` - synthesise valid random blocks directly (multi-GB models; no float tensors exist).
+"""
+from __future__ import annotations
+
+import os
+
+import numpy as np
+
+from ..models.config import ModelConfig
+from .constants import BLOCK_GEOMETRY, FTYPE, GGMLType, TokenType, ValueType
+from .quants import quantize, random_blocks
+from .writer import GGUFWriter
+
+
+def use_more_bits(i_layer: int, n_layer: int) -> bool:
+    return i_layer < n_layer // 8 or i_layer >= 7 * n_layer // 8 or (i_layer - n_layer // 8) % 3 == 2
+
+
+def tensor_type_for(name: str, ftype: str, i_layer: int, cfg: ModelConfig) -> GGMLType:
+    """Per-tensor storage type for a given file type."""
+    if name.endswith("_norm.weight") or name == "rope_freqs.weight" or name.endswith("ffn_gate_inp.weight"):
+        return GGMLType.F32
+    if ftype == "F32":
+        return GGMLType.F32
+    if ftype == "F16":
+        return GGMLType.F16
+    if ftype == "BF16":
+        return GGMLType.BF16
+    if ftype == "Q8_0":
+        return GGMLType.Q8_0
+    if ftype == "Q6_K":
+        return GGMLType.Q6_K
+    if ftype in ("Q4_K_M", "Q5_K_M"):
+        base = GGMLType.Q4_K if ftype == "Q4_K_M" else GGMLType.Q5_K
+        if name == "output.weight":
+            return GGMLType.Q6_K
+        if name == "token_embd.weight":
+            return base
+        if ".attn_v." in name:
+            if use_more_bits(i_layer, cfg.n_layer):
+                return GGMLType.Q6_K
+            if cfg.n_layer >= 80 and base == GGMLType.Q4_K:  # 70B: shared KV heads get Q5_K
+                return GGMLType.Q5_K
+            return base
+        if ".ffn_down" in name and use_more_bits(i_layer, cfg.n_layer):
+            return GGMLType.Q6_K
+        return base
+    raise ValueError(f"unknown file type {ftype!r}")
+
+
+def synthetic_vocab(n_vocab: int) -> tuple[list[str], np.ndarray, np.ndarray]:
+    """A self-consistent SentencePiece-style vocabulary: specials, 256 byte tokens, then word pieces."""
+    tokens = ["<unk>", "<s>", "</s>"]
+    types = [TokenType.UNKNOWN, TokenType.CONTROL, TokenType.CONTROL]
+    scores = [0.0, 0.0, 0.0]
+    for b in range(256):
+        tokens.append(f"<0x{b:02X}>")
+        types.append(TokenType.BYTE)
+        scores.append(0.0)
+    syll = ["a", "e", "i", "o", "u", "ka", "ri", "to", "me", "su", "no", "la", "ve", "di", "po", "an", "er", "is",
+            "th", "in", "on", "st", "ch", "qu", "ly", "ng", "ed", "es", "or", "al"]
+    singles = [chr(c) for c in range(32, 127)]
+    idx = 0
+    while len(tokens) < n_vocab:
+        if idx < len(singles):
+            piece = singles[idx]
+            piece = "▁" if piece == " " else piece
+        else:
+            k = idx - len(singles)
+            parts = []
+            n = k
+            for _ in range(1 + (k % 3)):
+                parts.append(syll[n % len(syll)])
+                n //= len(syll)
+            piece = ("▁" if k % 2 == 0 else "") + "".join(parts) + (str(k) if k >= len(syll) ** 2 else "")
+        idx += 1
+        if piece in ("<unk>", "<s>", "</s>"):
+            continue
+        tokens.append(piece)
+        types.append(TokenType.NORMAL)
+        scores.append(-float(len(tokens)))
+    # de-duplicate while preserving count
+    seen: dict[str, int] = {}
+    for i, t in enumerate(tokens):
+        if t in seen:
+            tokens[i] = f"{t}#{i}"
+        seen[tokens[i]] = i
+    return tokens[:n_vocab], np.asarray(scores[:n_vocab], np.float32), np.asarray(types[:n_vocab], np.int32)
+
+
+def _tensor_plan(cfg: ModelConfig, rope_freqs: bool):
+    """(name, shape, layer, init_std) for every tensor of the architecture; shapes row-major [out, in]."""
+    E, F = cfg.n_embd, cfg.n_ff
+    plan = [("token_embd.weight", (cfg.vocab_size, E), -1, 0.02)]
+    if rope_freqs:
+        plan.append(("rope_freqs.weight", (cfg.rope_dim // 2,), -1, 0.0))
+    for il in range(cfg.n_layer):
+        p = f"blk.{il}."
+        plan += [
+            (p + "attn_norm.weight", (E,), il, 0.0),
+            (p + "attn_q.weight", (cfg.q_dim, E), il, 0.02),
+            (p + "attn_k.weight", (cfg.kv_dim, E), il, 0.02),
+            (p + "attn_v.weight", (cfg.kv_dim, E), il, 0.02),
+            (p + "attn_output.weight", (E, cfg.q_dim), il, 0.02),
+            (p + "ffn_norm.weight", (E,), il, 0.0),
+        ]
+        if cfg.is_moe:
+            plan += [
+                (p + "ffn_gate_inp.weight", (cfg.n_expert, E), il, 0.02),
+                (p + "ffn_gate_exps.weight", (cfg.n_expert, F, E), il, 0.02),
+                (p + "ffn_down_exps.weight", (cfg.n_expert, E, F), il, 0.02),
+                (p + "ffn_up_exps.weight", (cfg.n_expert, F, E), il, 0.02),
+            ]
+        else:
+            plan += [
+                (p + "ffn_gate.weight", (F, E), il, 0.02),
+                (p + "ffn_down.weight", (E, F), il, 0.02),
+                (p + "ffn_up.weight", (F, E), il, 0.02),
+            ]
+    plan.append(("output_norm.weight", (E,), -1, 0.0))
+    if not cfg.tie_embeddings:
+        plan.append(("output.weight", (cfg.vocab_size, E), -1, 0.02))
+    return plan
+
+
+def write_synthetic_gguf(path: str, cfg: ModelConfig, ftype: str = "F16", seed: int = 0, exact: bool | None = None,
+                         rope_freqs: bool = False, vocab: bool = True) -> str:
+    """Write a random-init checkpoint for `cfg` at `path` and return the path."""
+    if exact is None:
+        exact = cfg.n_params() < 300_000_000
+    os.makedirs(os.path.dirname(os.path.abspath(path)), exist_ok=True)
+    w = GGUFWriter(path)
+    a = cfg.arch
+    w.add("general.architecture", a)
+    w.add("general.name", f"{cfg.name}-random-init")
+    w.add("general.file_type", FTYPE[ftype], ValueType.UINT32)
+    w.add("general.quantization_version", 2, ValueType.UINT32)
+    w.add(f"{a}.vocab_size", cfg.vocab_size, ValueType.UINT32)
+    w.add(f"{a}.context_length", cfg.n_ctx_train, ValueType.UINT32)
+    w.add(f"{a}.embedding_length", cfg.n_embd, ValueType.UINT32)
+    w.add(f"{a}.block_count", cfg.n_layer, ValueType.UINT32)
+    w.add(f"{a}.feed_forward_length", cfg.n_ff, ValueType.UINT32)
+    w.add(f"{a}.attention.head_count", cfg.n_head, ValueType.UINT32)
+    w.add(f"{a}.attention.head_count_kv", cfg.n_head_kv, ValueType.UINT32)
+    w.add(f"{a}.attention.layer_norm_rms_epsilon", float(cfg.rms_eps), ValueType.FLOAT32)
+    w.add(f"{a}.rope.freq_base", float(cfg.rope_theta), ValueType.FLOAT32)
+    w.add(f"{a}.rope.dimension_count", cfg.rope_dim, ValueType.UINT32)
+    if cfg.head_dim * cfg.n_head != cfg.n_embd:
+        w.add(f"{a}.attention.key_length", cfg.head_dim, ValueType.UINT32)
+        w.add(f"{a}.attention.value_length", cfg.head_dim, ValueType.UINT32)
+    if cfg.is_moe:
+        w.add(f"{a}.expert_count", cfg.n_expert, ValueType.UINT32)
+        w.add(f"{a}.expert_used_count", cfg.n_expert_used, ValueType.UINT32)
+    if vocab:
+        toks, scores, types = synthetic_vocab(cfg.vocab_size)
+        w.add("tokenizer.ggml.model", "llama")
+        w.add("tokenizer.ggml.pre", "default")
+        w.add("tokenizer.ggml.tokens", toks, etype=ValueType.STRING)
+        w.add("tokenizer.ggml.scores", scores, etype=ValueType.FLOAT32)
+        w.add("tokenizer.ggml.token_type", types, etype=ValueType.INT32)
+        w.add("tokenizer.ggml.bos_token_id", 1, ValueType.UINT32)
+        w.add("tokenizer.ggml.eos_token_id", 2, ValueType.UINT32)
+        w.add("tokenizer.ggml.unknown_token_id", 0, ValueType.UINT32)
+        w.add("tokenizer.ggml.add_bos_token", True)
+        w.add("tokenizer.ggml.add_eos_token", False)
+
+    pools: dict = {}
+
+    def make_producer(name, shape, il, std, ttype, tseed):
+        def produce():
+            rng = np.random.default_rng(tseed)
+            n = int(np.prod(shape))
+            if std == 0.0:
+                if name == "rope_freqs.weight":
+                    return np.ones(shape, np.float32).view(np.uint8).reshape(-1)
+                return (1.0 + 0.1 * rng.standard_normal(n, dtype=np.float32)).astype("<f4").view(np.uint8)
+            if exact:
+                x = rng.standard_normal(n, dtype=np.float32) * std
+                return quantize(x.reshape(-1, shape[-1]), ttype)
+            # multi-GB checkpoints: draw one pool of valid random blocks per type and fill each tensor
+            # with a rotated tiling of it (bandwidth-bound instead of RNG-bound; still random-init)
+            per, nbytes = BLOCK_GEOMETRY[ttype]
+            pool_elems = 1 << 24
+            if n <= pool_elems:
+                return random_blocks(ttype, n, rng, std)
+            key = (ttype, std)
+            if key not in pools:
+                pools[key] = random_blocks(ttype, pool_elems, np.random.default_rng(seed + 77), std
+                                           ).reshape(-1, nbytes)
+            pool = pools[key]
+            shift = int(rng.integers(0, pool.shape[0]))
+            rolled = np.concatenate([pool[shift:], pool[:shift]])
+            return np.resize(rolled, (n // per, nbytes)).reshape(-1)
+        return produce
+
+    for i, (name, shape, il, std) in enumerate(_tensor_plan(cfg, rope_freqs)):
+        ttype = tensor_type_for(name, ftype, max(il, 0), cfg)
+        w.add_tensor(name, shape, ttype, make_producer(name, shape, il, std, ttype, seed * 100003 + i))
+    return w.write()

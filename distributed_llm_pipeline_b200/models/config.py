@@ -1,0 +1,126 @@
+"""Model hyper-parameters and presets.
+
+Parity: hparams are read from the same GGUF KV names the reference uses
+(`llama.cpp/src/llama-arch.cpp:128-268`); presets are public architecture facts (TinyLlama-1.1B,
+Llama-3-8B/70B, Mixtral-8x7B) for the five BASELINE.json configurations.
+"""
+from __future__ import annotations
+
+from dataclasses import asdict, dataclass, field, replace
+from typing import Any
+
+
+@dataclass(frozen=True)
+class ModelConfig:
+    name: str = "llama"
+    arch: str = "llama"
+    vocab_size: int = 32000
+    n_embd: int = 4096
+    n_layer: int = 32
+    n_head: int = 32
+    n_head_kv: int = 8
+    head_dim: int = 128
+    n_ff: int = 14336
+    n_ctx_train: int = 8192
+    rms_eps: float = 1e-5
+    rope_theta: float = 500000.0
+    rope_dim: int = 128
+    rope_neox: bool = False  # llama arch = adjacent-pair ("norm") rotation
+    rope_scale_linear: float = 1.0
+    n_expert: int = 0
+    n_expert_used: int = 0
+    bos_id: int = 1
+    eos_id: int = 2
+    tie_embeddings: bool = False
+
+    @property
+    def n_gqa(self) -> int:
+        return self.n_head // self.n_head_kv
+
+    @property
+    def q_dim(self) -> int:
+        return self.n_head * self.head_dim
+
+    @property
+    def kv_dim(self) -> int:
+        return self.n_head_kv * self.head_dim
+
+    @property
+    def is_moe(self) -> bool:
+        return self.n_expert > 0
+
+    def n_params(self) -> int:
+        attn = self.n_embd * (self.q_dim + 2 * self.kv_dim) + self.q_dim * self.n_embd
+        ffn = 3 * self.n_embd * self.n_ff * max(1, self.n_expert) + (self.n_embd * self.n_expert if self.is_moe else 0)
+        emb = self.vocab_size * self.n_embd * (1 if self.tie_embeddings else 2)
+        return self.n_layer * (attn + ffn + 2 * self.n_embd) + emb + self.n_embd
+
+    def to_dict(self) -> dict[str, Any]:
+        return asdict(self)
+
+
+PRESETS: dict[str, ModelConfig] = {
+    # tiny shapes for CPU tests / smoke
+    "tiny": ModelConfig(name="tiny", vocab_size=512, n_embd=256, n_layer=2, n_head=4, n_head_kv=2, head_dim=64,
+                        n_ff=512, n_ctx_train=512, rope_theta=10000.0, rope_dim=64),
+    "tiny128": ModelConfig(name="tiny128", vocab_size=1024, n_embd=512, n_layer=2, n_head=4, n_head_kv=2,
+                           head_dim=128, n_ff=1024, n_ctx_train=1024, rope_theta=10000.0, rope_dim=128),
+    "tiny-moe": ModelConfig(name="tiny-moe", vocab_size=512, n_embd=256, n_layer=2, n_head=4, n_head_kv=2,
+                            head_dim=64, n_ff=256, n_ctx_train=512, rope_theta=10000.0, rope_dim=64, n_expert=4,
+                            n_expert_used=2),
+    "tinyllama-1.1b": ModelConfig(name="tinyllama-1.1b", vocab_size=32000, n_embd=2048, n_layer=22, n_head=32,
+                                  n_head_kv=4, head_dim=64, n_ff=5632, n_ctx_train=2048, rope_theta=10000.0,
+                                  rope_dim=64),
+    "llama-3-8b": ModelConfig(name="llama-3-8b", vocab_size=128256, n_embd=4096, n_layer=32, n_head=32, n_head_kv=8,
+                              head_dim=128, n_ff=14336, n_ctx_train=8192, rope_theta=500000.0, rope_dim=128,
+                              bos_id=128000, eos_id=128001),
+    "llama-3-70b": ModelConfig(name="llama-3-70b", vocab_size=128256, n_embd=8192, n_layer=80, n_head=64,
+                               n_head_kv=8, head_dim=128, n_ff=28672, n_ctx_train=8192, rope_theta=500000.0,
+                               rope_dim=128, bos_id=128000, eos_id=128001),
+    "mixtral-8x7b": ModelConfig(name="mixtral-8x7b", vocab_size=32000, n_embd=4096, n_layer=32, n_head=32,
+                                n_head_kv=8, head_dim=128, n_ff=14336, n_ctx_train=32768, rope_theta=1000000.0,
+                                rope_dim=128, n_expert=8, n_expert_used=2),
+}
+
+
+def preset(name: str, **overrides) -> ModelConfig:
+    if name not in PRESETS:
+        raise KeyError(f"unknown model preset {name!r}; known: {sorted(PRESETS)}")
+    return replace(PRESETS[name], **overrides)
+
+
+def config_from_gguf(meta: dict[str, Any], tensors: dict | None = None) -> ModelConfig:
+    """Build a ModelConfig from GGUF metadata (keys as in `llama-arch.cpp:128-268`)."""
+    arch = meta.get("general.architecture", "llama")
+    if arch != "llama":
+        raise NotImplementedError(f"architecture {arch!r} not supported (llama / mixtral-as-llama only)")
+
+    def g(key, default=None):
+        return meta.get(f"{arch}.{key}", default)
+
+    n_embd = int(g("embedding_length"))
+    n_head = int(g("attention.head_count"))
+    n_head_kv = int(g("attention.head_count_kv", n_head))
+    head_dim = int(g("attention.key_length", n_embd // n_head))
+    vocab = g("vocab_size")
+    if vocab is None:
+        toks = meta.get("tokenizer.ggml.tokens")
+        if toks is not None:
+            vocab = len(toks)
+        elif tensors is not None and "token_embd.weight" in tensors:
+            vocab = tensors["token_embd.weight"].shape[0]
+        else:
+            raise ValueError("cannot determine vocab size")
+    scale = 1.0
+    if meta.get(f"{arch}.rope.scaling.type", "none") == "linear":
+        scale = 1.0 / float(meta.get(f"{arch}.rope.scaling.factor", 1.0))
+    tie = tensors is not None and "output.weight" not in tensors
+    return ModelConfig(
+        name=str(meta.get("general.name", arch)), arch=arch, vocab_size=int(vocab), n_embd=n_embd,
+        n_layer=int(g("block_count")), n_head=n_head, n_head_kv=n_head_kv, head_dim=head_dim,
+        n_ff=int(g("feed_forward_length")), n_ctx_train=int(g("context_length", 2048)),
+        rms_eps=float(g("attention.layer_norm_rms_epsilon", 1e-5)), rope_theta=float(g("rope.freq_base", 10000.0)),
+        rope_dim=int(g("rope.dimension_count", head_dim)), rope_neox=False, rope_scale_linear=scale,
+        n_expert=int(g("expert_count", 0) or 0), n_expert_used=int(g("expert_used_count", 0) or 0),
+        bos_id=int(meta.get("tokenizer.ggml.bos_token_id", 1)), eos_id=int(meta.get("tokenizer.ggml.eos_token_id", 2)),
+        tie_embeddings=tie)

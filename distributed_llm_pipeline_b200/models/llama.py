@@ -1,0 +1,392 @@
+"""Llama / Mixtral executor: paged KV cache, prefill + decode step functions, CUDA-graph decode.
+
+Parity: this is the `llama_context` decode loop (`llama.cpp/src/llama-context.cpp:1042-1104,1375-1724`) plus the
+graph `llm_build_llama` builds per ubatch (`llama.cpp/src/models/llama.cpp:31-164`), restated B200-first:
+there is no graph builder / scheduler / allocator at run time - the step is a fixed sequence of fused kernels
+over pre-allocated buffers (captured once into a CUDA graph per decode batch size), the KV cache is paged
+instead of a contiguous ring (`llama-kv-cache.cpp:100-150`), positions / slots advance on the device, and
+sampling happens on the device so only token ids cross PCIe.
+
+One engine instance = one (pipeline stage, tensor-parallel rank).  `comm` supplies the TP reduction and the
+PP activation hand-off (see parallel/).
+"""
+from __future__ import annotations
+
+import math
+from dataclasses import dataclass, field
+
+import torch
+
+from ..ops import api as ops
+from .config import ModelConfig
+from .reference import rope_inv_freq
+from .weights import ModelWeights
+
+
+@dataclass
+class Sequence:
+    sid: int
+    length: int = 0
+    pages: list[int] = field(default_factory=list)
+
+
+class PagedKVCache:
+    """Fixed-size pages [n_pages, Hkv, page, D] per layer + a host-side free list and block table."""
+
+    def __init__(self, cfg: ModelConfig, layers, n_head_kv: int, n_pages: int, page_size: int, max_seqs: int,
+                 max_pages_per_seq: int, device):
+        self.page_size = page_size
+        self.n_pages = n_pages
+        self.max_pages = max_pages_per_seq
+        shape = (n_pages, n_head_kv, page_size, cfg.head_dim)
+        self.k = {il: torch.zeros(shape, dtype=torch.float16, device=device) for il in layers}
+        self.v = {il: torch.zeros(shape, dtype=torch.float16, device=device) for il in layers}
+        self.free = list(range(n_pages - 1, -1, -1))
+        self.block_table = torch.zeros(max_seqs, max_pages_per_seq, dtype=torch.int32, device=device)
+        self.block_table_host = torch.zeros(max_seqs, max_pages_per_seq, dtype=torch.int32)
+        if torch.device(device).type == "cuda":
+            self.block_table_host = self.block_table_host.pin_memory()
+
+    def ensure(self, seq: Sequence, new_len: int):
+        need = (new_len + self.page_size - 1) // self.page_size
+        if need > self.max_pages:
+            raise RuntimeError(f"sequence {seq.sid}: context {new_len} exceeds n_ctx")
+        grew = False
+        while len(seq.pages) < need:
+            if not self.free:
+                raise RuntimeError("KV cache exhausted (no free pages)")
+            pg = self.free.pop()
+            self.block_table_host[seq.sid, len(seq.pages)] = pg
+            seq.pages.append(pg)
+            grew = True
+        if grew:
+            self.block_table[seq.sid].copy_(self.block_table_host[seq.sid], non_blocking=True)
+
+    def release(self, seq: Sequence):
+        self.free.extend(reversed(seq.pages))
+        seq.pages.clear()
+        seq.length = 0
+
+    def bytes(self) -> int:
+        return sum(t.numel() * 2 for t in self.k.values()) * 2
+
+
+class NullComm:
+    """Single-rank communicator (tp = pp = 1)."""
+    tp_size = 1
+    tp_rank = 0
+
+    def allreduce_delta(self, delta, il, which):
+        return delta
+
+    def allgather_logits(self, logits, vocab_range, vocab_size):
+        return logits
+
+    fused = False
+
+
+class LlamaEngine:
+    def __init__(self, weights: ModelWeights, n_ctx: int = 4096, max_seqs: int = 8, page_size: int = 64,
+                 max_batch_tokens: int = 2048, n_pages: int | None = None, comm=None, first_stage: bool = True,
+                 last_stage: bool = True, attn_splits: int | None = None):
+        self.w = weights
+        self.cfg = cfg = weights.cfg
+        dev = (weights.tok_embd or weights.lm_head or next(iter(weights.layers.values())).wqkv).device
+        self.device = dev
+        self.comm = comm or NullComm()
+        self.first_stage, self.last_stage = first_stage, last_stage
+        self.n_ctx, self.max_seqs, self.page_size = n_ctx, max_seqs, page_size
+        self.max_tokens = max(max_batch_tokens, max_seqs)
+        self.Hq, self.Hkv, self.D = weights.n_head_local, weights.n_head_kv_local, cfg.head_dim
+        self.E, self.F = cfg.n_embd, weights.n_ff_local
+        max_pages = (n_ctx + page_size - 1) // page_size
+        if n_pages is None:
+            n_pages = max_pages * max_seqs
+        self.kv = PagedKVCache(cfg, weights.layer_range, self.Hkv, n_pages, page_size, max_seqs, max_pages, dev)
+        self.inv_freq = rope_inv_freq(cfg, weights.rope_freqs.cpu() if weights.rope_freqs is not None else None).to(dev)
+        self.seqs: dict[int, Sequence] = {}
+        self._free_sids = list(range(max_seqs - 1, -1, -1))
+        M = self.max_tokens
+        f16, f32, i32 = torch.float16, torch.float32, torch.int32
+        qkv_dim = (self.Hq + 2 * self.Hkv) * self.D
+        self.h = torch.zeros(M, self.E, dtype=f32, device=dev)
+        self.delta = torch.zeros(M, self.E, dtype=f32, device=dev)
+        self.xn = torch.zeros(M, self.E, dtype=f16, device=dev)
+        self.qkv32 = torch.zeros(min(M, 4), qkv_dim, dtype=f32, device=dev)
+        self.qkv16 = torch.zeros(M, qkv_dim, dtype=f16, device=dev)
+        self.q = torch.zeros(M, self.Hq * self.D, dtype=f16, device=dev)
+        self.att = torch.zeros(M, self.Hq * self.D, dtype=f16, device=dev)
+        self.act = torch.zeros(M, self.F, dtype=f16, device=dev)
+        self.tokens = torch.zeros(M, dtype=i32, device=dev)
+        self.pos = torch.zeros(M, dtype=i32, device=dev)
+        self.slot = torch.zeros(M, dtype=i32, device=dev)
+        self.kv_len = torch.zeros(M, dtype=i32, device=dev)
+        self.bt_row = torch.zeros(M, dtype=i32, device=dev)
+        self.seq_len_dev = torch.zeros(max_seqs, dtype=i32, device=dev)
+        self.next_tok = torch.zeros(max_seqs, dtype=i32, device=dev)
+        self.step_ctr = torch.zeros(1, dtype=i32, device=dev)
+        v0, v1 = weights.vocab_range
+        self.logits = torch.zeros(max_seqs, v1 - v0, dtype=f32, device=dev) if last_stage else None
+        self.attn_splits = attn_splits if attn_splits is not None else (16 if dev.type == "cuda" else 1)
+        ns = self.attn_splits
+        self.attn_ws = (torch.zeros(max_seqs * self.Hq * ns * self.D, dtype=f32, device=dev),
+                        torch.zeros(max_seqs * self.Hq * ns * 2, dtype=f32, device=dev)) if ns > 1 else None
+        self.scratch = None  # fp16 decode buffer for block-quantised weights on the GEMM path (allocated lazily)
+        self._graphs: dict[tuple, torch.cuda.CUDAGraph] = {}
+        self.sampling = dict(top_k=40, top_p=0.95, min_p=0.05, temp=0.0, seed=0)
+
+    # ---- sequence management ------------------------------------------------------------------
+    def alloc_seq(self) -> int:
+        if not self._free_sids:
+            raise RuntimeError("no free sequence slots")
+        sid = self._free_sids.pop()
+        self.seqs[sid] = Sequence(sid)
+        return sid
+
+    def free_seq(self, sid: int):
+        self.kv.release(self.seqs.pop(sid))
+        self._free_sids.append(sid)
+
+    def seq_len(self, sid: int) -> int:
+        return self.seqs[sid].length
+
+    def _scratch_for(self, *ws):
+        need = 0
+        for w in ws:
+            if w is not None and w.dense is None and w.wtype.name.startswith("Q"):
+                need += w.N * w.K * 2
+        if need == 0:
+            return None
+        if self.scratch is None or self.scratch.numel() < need:
+            self.scratch = torch.empty(need, dtype=torch.uint8, device=self.device)
+        return self.scratch
+
+    # ---- one transformer layer over T tokens held in the static buffers ------------------------
+    def _layer(self, il: int, T: int, attn_fn):
+        lw, cfg, comm = self.w.layers[il], self.cfg, self.comm
+        h = self.h[:T]
+        tp = comm.tp_size > 1
+        small = T <= 4 and not tp  # fused mat-vec path (norm in prologue, residual add in epilogue)
+        # --- attention block ---
+        if small:
+            qkv = ops.linear(lw.wqkv, h, "f32", norm_w=lw.attn_norm, eps=cfg.rms_eps, out=self.qkv32[:T])
+        else:
+            xn = ops.rmsnorm(h, lw.attn_norm, cfg.rms_eps, out=self.xn[:T])
+            qkv = ops.linear(lw.wqkv, xn, "f16", out=self.qkv16[:T], scratch=self._scratch_for(lw.wqkv))
+        q = ops.rope_kv(qkv, self.pos[:T], self.slot[:T], self.inv_freq, self.kv.k[il], self.kv.v[il], self.Hq, self.Hkv,
+                        self.D, cfg.rope_neox, q_out=self.q[:T])
+        att = attn_fn(il, q, T)
+        if tp:
+            d = ops.linear(lw.wo, att, "f32", out=self.delta[:T], scratch=self._scratch_for(lw.wo))
+            d = comm.allreduce_delta(d, il, 0)
+            xn = ops.rmsnorm(h, lw.ffn_norm, cfg.rms_eps, delta=d, out=self.xn[:T])
+        elif small:
+            ops.linear(lw.wo, att, "add", out=h)
+        else:
+            ops.linear(lw.wo, att, "add", out=h, scratch=self._scratch_for(lw.wo))
+            xn = ops.rmsnorm(h, lw.ffn_norm, cfg.rms_eps, out=self.xn[:T])
+        # --- feed-forward block ---
+        if cfg.is_moe:
+            self._moe(lw, T, None if small else xn)
+            return
+        if small:
+            act = ops.linear(lw.w_gate, h, "swiglu", w_up=lw.w_up, norm_w=lw.ffn_norm, eps=cfg.rms_eps, out=self.act[:T])
+            ops.linear(lw.w_down, act, "add", out=h)
+            return
+        act = ops.linear(lw.w_gate, xn, "swiglu", w_up=lw.w_up, out=self.act[:T], scratch=self._scratch_for(lw.w_gate, lw.w_up))
+        if tp:
+            d = ops.linear(lw.w_down, act, "f32", out=self.delta[:T], scratch=self._scratch_for(lw.w_down))
+            d = comm.allreduce_delta(d, il, 1)
+            h.add_(d)
+        else:
+            ops.linear(lw.w_down, act, "add", out=h, scratch=self._scratch_for(lw.w_down))
+
+    def _moe(self, lw, T: int, xn):
+        """Top-k routed experts (softmax over all experts, top-k, renormalise: llama-graph.cpp:1039-1139).
+        Round-1 implementation: router + expert selection on the host side of the stream (not graph-capturable)."""
+        cfg, comm = self.cfg, self.comm
+        h = self.h[:T]
+        if xn is None:
+            xn = ops.rmsnorm(h, lw.ffn_norm, cfg.rms_eps, out=self.xn[:T])
+        logits = xn.float() @ lw.router.T
+        probs = torch.softmax(logits, -1)
+        topw, topi = probs.topk(cfg.n_expert_used, -1)
+        topw = topw / topw.sum(-1, keepdim=True)
+        out = torch.zeros(T, self.E, dtype=torch.float32, device=h.device)
+        topi_h = topi.cpu()
+        for e in torch.unique(topi_h).tolist():
+            rows = (topi_h == e).any(-1).nonzero().flatten().to(h.device)
+            xe = xn[rows].contiguous()
+            act = ops.linear(lw.e_gate[e], xe, "swiglu", w_up=lw.e_up[e], scratch=self._scratch_for(lw.e_gate[e], lw.e_up[e]))
+            ye = ops.linear(lw.e_down[e], act, "f32", scratch=self._scratch_for(lw.e_down[e]))
+            we = (topw[rows] * (topi[rows] == e)).sum(-1, keepdim=True)
+            out.index_add_(0, rows, we * ye)
+        if comm.tp_size > 1:
+            out = comm.allreduce_delta(out, -1, 1)
+        h.add_(out)
+
+    # ---- attention flavours ---------------------------------------------------------------------
+    def _attn_decode(self, il, q, T):
+        return ops.attn_paged(q, self.kv.k[il], self.kv.v[il], self.kv.block_table, self.kv_len[:T], self.Hq, self.Hkv,
+                              self.D, bt_row=self.bt_row[:T], n_splits=self.attn_splits if T <= self.max_seqs else 1,
+                              workspace=self.attn_ws if T <= self.max_seqs else None, out=self.att[:T])
+
+    def _attn_prefill_for(self, sid: int, pos0: int):
+        def fn(il, q, T):
+            return ops.attn_prefill(q, self.kv.k[il], self.kv.v[il], self.kv.block_table[sid], pos0, self.Hq, self.Hkv,
+                                    self.D, out=self.att[:T])
+        return fn
+
+    # ---- stage-level forward ------------------------------------------------------------------
+    def _embed(self, T: int, ids: torch.Tensor | None = None):
+        ops.dequant_rows(self.w.tok_embd, self.tokens[:T] if ids is None else ids, out=self.h[:T])
+
+    def _run_layers(self, T: int, attn_fn):
+        for il in self.w.layer_range:
+            self._layer(il, T, attn_fn)
+
+    def _head(self, rows: torch.Tensor | slice, n: int) -> torch.Tensor:
+        """logits for `n` rows of h (already gathered to the front of the xn buffer) -> self.logits[:n]."""
+        cfg = self.cfg
+        hsel = self.h[rows]
+        if n <= 4 and n != 3:
+            lg = ops.linear(self.w.lm_head, hsel.contiguous(), "f32", norm_w=self.w.out_norm, eps=cfg.rms_eps, out=self.logits[:n])
+        else:
+            xn = ops.rmsnorm(hsel.contiguous(), self.w.out_norm, cfg.rms_eps)
+            lg = ops.linear(self.w.lm_head, xn, "f32", out=self.logits[:n], scratch=self._scratch_for(self.w.lm_head))
+        return self.comm.allgather_logits(lg, self.w.vocab_range, cfg.vocab_size)
+
+    # ---- public: prefill ------------------------------------------------------------------------
+    @torch.no_grad()
+    def prefill(self, sid: int, tokens, hidden_in: torch.Tensor | None = None, chunk: int | None = None):
+        """Append `tokens` to sequence `sid`.  Returns logits [vocab] of the last token (last stage) or the
+        hidden states [T, E] to hand to the next pipeline stage."""
+        seq = self.seqs[sid]
+        tokens = torch.as_tensor(tokens, dtype=torch.int32)
+        n = tokens.numel()
+        chunk = min(chunk or self.max_tokens, self.max_tokens)
+        outs = []
+        for c0 in range(0, n, chunk):
+            T = min(chunk, n - c0)
+            pos0 = seq.length
+            self.kv.ensure(seq, pos0 + T)
+            pos = torch.arange(pos0, pos0 + T, dtype=torch.int32)
+            pages = torch.tensor(seq.pages, dtype=torch.int32)
+            slot = pages[(pos // self.page_size).long()] * self.page_size + pos % self.page_size
+            self.pos[:T].copy_(pos, non_blocking=True)
+            self.slot[:T].copy_(slot.to(torch.int32), non_blocking=True)
+            if self.first_stage:
+                self.tokens[:T].copy_(tokens[c0:c0 + T], non_blocking=True)
+                self._embed(T)
+            else:
+                self.h[:T].copy_(hidden_in[c0:c0 + T])
+            self._run_layers(T, self._attn_prefill_for(sid, pos0))
+            seq.length = pos0 + T
+            if not self.last_stage:
+                outs.append(self.h[:T].clone())
+        self.seq_len_dev[sid] = seq.length
+        if not self.last_stage:
+            return torch.cat(outs, 0)
+        return self._head(slice(T - 1, T), 1)[0]
+
+    # ---- public: decode -------------------------------------------------------------------------
+    def _decode_body(self, B: int, sample: bool):
+        """One decode step for the sequences in slots bt_row[:B]; everything stays on the device."""
+        ops.advance(self._seq_len_view, self.pos[:B], self.slot[:B], self._bt_view, self.page_size)
+        self.kv_len[:B].copy_(self._seq_len_view)  # after advance: length including the new token
+        if self.first_stage:
+            self._embed(B, self.next_tok[:B])  # input ids = previously sampled (or host-provided) tokens
+        self._run_layers(B, self._attn_decode)
+        if self.last_stage:
+            lg = self._head(slice(0, B), B)
+            if sample:
+                s = self.sampling
+                ops.sample(lg, s["top_k"], s["top_p"], s["min_p"], s["temp"], s["seed"], self.step_ctr, out=self.next_tok[:B])
+                self.step_ctr.add_(1)
+
+    @torch.no_grad()
+    def decode(self, sids: list[int], tokens=None, hidden_in: torch.Tensor | None = None, sample: bool = True,
+               use_graph: bool = True):
+        """One token for each sequence in `sids` (which must occupy slots 0..B-1 for the graph path).
+        tokens: host ints / tensor, or None to feed back the previously sampled tokens (device resident).
+        Returns next-token ids (device int32 [B]) when sampling, else logits [B, vocab]; or hidden states."""
+        B = len(sids)
+        for sid in sids:
+            seq = self.seqs[sid]
+            self.kv.ensure(seq, seq.length + 1)
+        contiguous = sids == list(range(B))
+        if contiguous:
+            self._seq_len_view, self._bt_view = self.seq_len_dev[:B], self.kv.block_table[:B]
+            if not getattr(self, "_bt_row_iota", 0) >= B:
+                self.bt_row[:self.max_seqs].copy_(torch.arange(self.max_seqs, dtype=torch.int32))
+                self._bt_row_iota = self.max_seqs
+        else:
+            idx = torch.tensor(sids, dtype=torch.long, device=self.device)
+            self._seq_len_view, self._bt_view = self.seq_len_dev[idx], self.kv.block_table[idx].contiguous()
+            self.bt_row[:B].copy_(torch.arange(B, dtype=torch.int32))
+            self._bt_row_iota = 0
+        if tokens is not None and self.first_stage:
+            self.next_tok[:B].copy_(torch.as_tensor(tokens, dtype=torch.int32), non_blocking=True)
+        if hidden_in is not None:
+            self.h[:B].copy_(hidden_in)
+        graphable = (use_graph and contiguous and self.device.type == "cuda" and not self.cfg.is_moe
+                     and not getattr(self.comm, "no_graph", False))
+        if graphable:
+            key = (B, sample)
+            g = self._graphs.get(key)
+            if g is None:
+                g = self._capture(B, sample)
+            g.replay()
+        else:
+            self._decode_body(B, sample)
+            if not contiguous:
+                self.seq_len_dev[idx] = self._seq_len_view
+        for sid in sids:
+            self.seqs[sid].length += 1
+        if not self.last_stage:
+            return self.h[:B]
+        return self.next_tok[:B] if sample else self.logits[:B]
+
+    def _capture(self, B: int, sample: bool):
+        # warm-up (also lets every kernel set its attributes), then roll back the bookkeeping it advanced
+        saved = self.seq_len_dev.clone()
+        saved_ctr = self.step_ctr.clone()
+        s = torch.cuda.Stream()
+        s.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(s):
+            self._decode_body(B, sample)
+        torch.cuda.current_stream().wait_stream(s)
+        self.seq_len_dev.copy_(saved)
+        self.step_ctr.copy_(saved_ctr)
+        g = torch.cuda.CUDAGraph()
+        n0 = ops.launch_count
+        with torch.cuda.graph(g):
+            self._decode_body(B, sample)
+        self.launches_per_graph = getattr(self, "launches_per_graph", {})
+        self.launches_per_graph[(B, sample)] = ops.launch_count - n0
+        self.seq_len_dev.copy_(saved)
+        self.step_ctr.copy_(saved_ctr)
+        self._graphs[(B, sample)] = g
+        return g
+
+    # ---- convenience ------------------------------------------------------------------------------
+    @torch.no_grad()
+    def generate(self, prompt: list[int], n_predict: int, sid: int | None = None, stop_ids: tuple[int, ...] = ()):
+        """Greedy / sampled generation for one sequence (slot 0 path); returns the generated ids."""
+        own = sid is None
+        if own:
+            sid = self.alloc_seq()
+        logits = self.prefill(sid, prompt)
+        s = self.sampling
+        tok = (ops.argmax(logits[None]) if s["temp"] <= 0 else
+               ops.sample(logits[None], s["top_k"], s["top_p"], s["min_p"], s["temp"], s["seed"], self.step_ctr))
+        self.next_tok[:1].copy_(tok)
+        out = [int(tok[0])]
+        for _ in range(n_predict - 1):
+            if out[-1] in stop_ids:
+                break
+            nt = self.decode([sid], use_graph=(sid == 0))
+            out.append(int(nt[0]))
+        if own:
+            self.free_seq(sid)
+        return out

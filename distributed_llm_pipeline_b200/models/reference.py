@@ -1,0 +1,187 @@
+"""FP32 PyTorch oracle for the llama / mixtral forward pass.
+
+This is the numerical reference every CUDA kernel and every parallel layout is tested against
+(NMSE metric and thresholds as in `llama.cpp/tests/test-backend-ops.cpp:273-287,3716-3718`), and the
+timed CPU baseline for config 1.  The graph it evaluates is the one the reference builds per ubatch
+(`llama.cpp/src/models/llama.cpp:31-164`): RMSNorm -> Wq/Wk/Wv -> RoPE(Q,K) -> KV write -> causal
+GQA attention -> Wo -> +res -> RMSNorm -> SwiGLU FFN | top-k MoE -> +res; final norm; lm_head.
+MoE routing matches `build_moe_ffn` (`llama.cpp/src/llama-graph.cpp:1039-1139`): softmax over all
+experts, top-k, re-normalised weights.
+"""
+from __future__ import annotations
+
+import math
+from dataclasses import dataclass, field
+
+import numpy as np
+import torch
+
+from ..gguf import GGUFModelFiles, open_gguf
+from .config import ModelConfig, config_from_gguf
+
+
+def nmse(a: torch.Tensor, b: torch.Tensor) -> float:
+    """Normalised mean squared error of `b` against reference `a`."""
+    a = a.detach().double().flatten().cpu()
+    b = b.detach().double().flatten().cpu()
+    return float(((a - b) ** 2).sum() / (a ** 2).sum().clamp_min(1e-30))
+
+
+def rope_inv_freq(cfg: ModelConfig, freq_factors: torch.Tensor | None = None) -> torch.Tensor:
+    i = torch.arange(0, cfg.rope_dim // 2, dtype=torch.float64)
+    inv = cfg.rope_theta ** (-2.0 * i / cfg.rope_dim) * cfg.rope_scale_linear
+    if freq_factors is not None:
+        inv = inv / freq_factors.double()
+    return inv.float()
+
+
+def apply_rope(x: torch.Tensor, pos: torch.Tensor, inv_freq: torch.Tensor, neox: bool) -> torch.Tensor:
+    """x: [T, H, D]; pos: [T]. Rotates the first 2*len(inv_freq) dims of every head."""
+    n_rot = inv_freq.numel() * 2
+    ang = pos.to(torch.float32)[:, None] * inv_freq[None, :]
+    cos = ang.cos()[:, None, :]
+    sin = ang.sin()[:, None, :]
+    xr = x[..., :n_rot]
+    if neox:
+        x0, x1 = xr[..., : n_rot // 2], xr[..., n_rot // 2:]
+        out = torch.cat([x0 * cos - x1 * sin, x0 * sin + x1 * cos], dim=-1)
+    else:
+        x0, x1 = xr[..., 0::2], xr[..., 1::2]
+        out = torch.stack([x0 * cos - x1 * sin, x0 * sin + x1 * cos], dim=-1).flatten(-2)
+    return torch.cat([out, x[..., n_rot:]], dim=-1)
+
+
+def rms_norm(x: torch.Tensor, w: torch.Tensor, eps: float) -> torch.Tensor:
+    return x * torch.rsqrt(x.pow(2).mean(-1, keepdim=True) + eps) * w
+
+
+@dataclass
+class RefKVCache:
+    k: list[torch.Tensor] = field(default_factory=list)  # per layer [n_ctx, Hkv, D]
+    v: list[torch.Tensor] = field(default_factory=list)
+    length: int = 0
+
+
+class ReferenceModel:
+    """Dense fp32 weights + eager forward.  Small models only (it dequantises everything)."""
+
+    def __init__(self, cfg: ModelConfig, weights: dict[str, torch.Tensor]):
+        self.cfg = cfg
+        self.w = weights
+        ff = weights.get("rope_freqs.weight")
+        self.inv_freq = rope_inv_freq(cfg, ff)
+
+    @classmethod
+    def from_gguf(cls, path_or_files: str | GGUFModelFiles) -> "ReferenceModel":
+        f = open_gguf(path_or_files) if isinstance(path_or_files, str) else path_or_files
+        cfg = config_from_gguf(f.metadata, f.tensors)
+        w = {name: torch.from_numpy(np.array(f.array(name), dtype=np.float32, copy=True)) for name in f.names()}
+        return cls(cfg, w)
+
+    def new_cache(self, n_ctx: int) -> RefKVCache:
+        c = self.cfg
+        return RefKVCache([torch.zeros(n_ctx, c.n_head_kv, c.head_dim) for _ in range(c.n_layer)],
+                          [torch.zeros(n_ctx, c.n_head_kv, c.head_dim) for _ in range(c.n_layer)], 0)
+
+    # ---- sub-blocks (exposed for per-op tests) --------------------------------------------
+    def attention(self, il: int, x: torch.Tensor, pos: torch.Tensor, cache: RefKVCache) -> torch.Tensor:
+        c, w = self.cfg, self.w
+        p = f"blk.{il}."
+        T = x.shape[0]
+        q = (x @ w[p + "attn_q.weight"].T).view(T, c.n_head, c.head_dim)
+        k = (x @ w[p + "attn_k.weight"].T).view(T, c.n_head_kv, c.head_dim)
+        v = (x @ w[p + "attn_v.weight"].T).view(T, c.n_head_kv, c.head_dim)
+        q = apply_rope(q, pos, self.inv_freq, c.rope_neox)
+        k = apply_rope(k, pos, self.inv_freq, c.rope_neox)
+        start = cache.length
+        cache.k[il][start:start + T] = k
+        cache.v[il][start:start + T] = v
+        K = cache.k[il][: start + T]
+        V = cache.v[il][: start + T]
+        Kx = K.repeat_interleave(c.n_gqa, dim=1)
+        Vx = V.repeat_interleave(c.n_gqa, dim=1)
+        scores = torch.einsum("thd,shd->hts", q, Kx) / math.sqrt(c.head_dim)
+        kpos = torch.arange(start + T)
+        mask = kpos[None, :] > pos[:, None]
+        scores = scores.masked_fill(mask[None], float("-inf"))
+        att = torch.softmax(scores, dim=-1)
+        o = torch.einsum("hts,shd->thd", att, Vx).reshape(T, c.q_dim)
+        return o @ w[p + "attn_output.weight"].T
+
+    def ffn(self, il: int, x: torch.Tensor) -> torch.Tensor:
+        c, w = self.cfg, self.w
+        p = f"blk.{il}."
+        if not c.is_moe:
+            g = x @ w[p + "ffn_gate.weight"].T
+            u = x @ w[p + "ffn_up.weight"].T
+            return (torch.nn.functional.silu(g) * u) @ w[p + "ffn_down.weight"].T
+        logits = x @ w[p + "ffn_gate_inp.weight"].T
+        probs = torch.softmax(logits, dim=-1)
+        topw, topi = probs.topk(c.n_expert_used, dim=-1)
+        topw = topw / topw.sum(-1, keepdim=True)
+        out = torch.zeros_like(x)
+        for e in range(c.n_expert):
+            sel = (topi == e)
+            rows = sel.any(-1).nonzero().flatten()
+            if rows.numel() == 0:
+                continue
+            xe = x[rows]
+            g = xe @ w[p + "ffn_gate_exps.weight"][e].T
+            u = xe @ w[p + "ffn_up_exps.weight"][e].T
+            y = (torch.nn.functional.silu(g) * u) @ w[p + "ffn_down_exps.weight"][e].T
+            we = (topw[rows] * sel[rows]).sum(-1, keepdim=True)
+            out[rows] += we * y
+        return out
+
+    def layer(self, il: int, h: torch.Tensor, pos: torch.Tensor, cache: RefKVCache) -> torch.Tensor:
+        c, w = self.cfg, self.w
+        p = f"blk.{il}."
+        h = h + self.attention(il, rms_norm(h, w[p + "attn_norm.weight"], c.rms_eps), pos, cache)
+        h = h + self.ffn(il, rms_norm(h, w[p + "ffn_norm.weight"], c.rms_eps))
+        return h
+
+    def embed(self, tokens: torch.Tensor) -> torch.Tensor:
+        return self.w["token_embd.weight"][tokens]
+
+    def head(self, h: torch.Tensor) -> torch.Tensor:
+        c, w = self.cfg, self.w
+        out_w = w.get("output.weight", w["token_embd.weight"])
+        return rms_norm(h, w["output_norm.weight"], c.rms_eps) @ out_w.T
+
+    # ---- full forward ---------------------------------------------------------------------
+    @torch.no_grad()
+    def forward(self, tokens, cache: RefKVCache, layers: range | None = None, hidden: torch.Tensor | None = None,
+                return_hidden: bool = False) -> torch.Tensor:
+        """Run `tokens` (appended at cache.length) through `layers` (default: all) and return logits
+        [T, vocab] - or the hidden state when this is a non-final pipeline stage."""
+        c = self.cfg
+        tokens = torch.as_tensor(tokens, dtype=torch.long)
+        T = tokens.numel()
+        pos = torch.arange(cache.length, cache.length + T)
+        layers = range(c.n_layer) if layers is None else layers
+        h = self.embed(tokens) if hidden is None else hidden
+        for il in layers:
+            h = self.layer(il, h, pos, cache)
+        last_stage = len(layers) == 0 or layers[-1] == c.n_layer - 1
+        if return_hidden or not last_stage:
+            return h
+        return self.head(h)
+
+    def advance(self, cache: RefKVCache, n: int):
+        cache.length += n
+
+    @torch.no_grad()
+    def generate_greedy(self, prompt: list[int], n_predict: int, n_ctx: int = 512) -> tuple[list[int], torch.Tensor]:
+        cache = self.new_cache(n_ctx)
+        logits = self.forward(prompt, cache)
+        self.advance(cache, len(prompt))
+        out = []
+        last = logits[-1]
+        all_logits = [last]
+        for _ in range(n_predict):
+            tok = int(last.argmax())
+            out.append(tok)
+            last = self.forward([tok], cache)[-1]
+            self.advance(cache, 1)
+            all_logits.append(last)
+        return out, torch.stack(all_logits)

@@ -1,0 +1,141 @@
+"""Shard-aware GGUF -> device weight loading for llama / mixtral checkpoints.
+
+Parity: replaces `llama_model::load_tensors` + `load_all_data` (`llama.cpp/src/llama-model.cpp:2465-2550`,
+`llama-model-loader.cpp:957-1197`).  The reference's client streams every tensor to its workers (RPC SET_TENSOR)
+or splits rows per device inside one process; here every rank opens the same mmapped file and uploads only
+  * the layers of its pipeline stage (layer ranges follow the reference's cumulative-split rule,
+    `llama-model.cpp:2492-2537`, see parallel/grid.py), and inside the stage
+  * its tensor-parallel slice: Wq/Wk/Wv/gate/up by output rows (column-parallel, whole heads per rank),
+    Wo/down by K range (row-parallel), lm_head by vocab rows.
+"""
+from __future__ import annotations
+
+from dataclasses import dataclass, field
+
+import numpy as np
+import torch
+
+from ..gguf import GGMLType, GGUFModelFiles, open_gguf
+from ..ops.weights import DeviceWeight, slice_raw, stack_rows
+from .config import ModelConfig, config_from_gguf
+
+
+@dataclass
+class LayerWeights:
+    attn_norm: torch.Tensor
+    wqkv: DeviceWeight
+    wo: DeviceWeight
+    ffn_norm: torch.Tensor
+    w_gate: DeviceWeight | None = None
+    w_up: DeviceWeight | None = None
+    w_down: DeviceWeight | None = None
+    # MoE
+    router: torch.Tensor | None = None                 # fp32 [n_expert, E]
+    e_gate: list[DeviceWeight] = field(default_factory=list)
+    e_up: list[DeviceWeight] = field(default_factory=list)
+    e_down: list[DeviceWeight] = field(default_factory=list)
+
+
+@dataclass
+class ModelWeights:
+    cfg: ModelConfig
+    layers: dict[int, LayerWeights]
+    layer_range: range
+    tp_rank: int
+    tp_size: int
+    tok_embd: DeviceWeight | None
+    out_norm: torch.Tensor | None
+    lm_head: DeviceWeight | None          # vocab rows [v0, v1) of the output matrix
+    vocab_range: tuple[int, int]
+    rope_freqs: torch.Tensor | None
+    n_head_local: int = 0
+    n_head_kv_local: int = 0
+    n_ff_local: int = 0
+
+    def nbytes(self) -> int:
+        tot = 0
+        for lw in self.layers.values():
+            for w in [lw.wqkv, lw.wo, lw.w_gate, lw.w_up, lw.w_down, *lw.e_gate, *lw.e_up, *lw.e_down]:
+                if w is not None:
+                    tot += w.nbytes
+        for w in (self.tok_embd, self.lm_head):
+            if w is not None:
+                tot += w.nbytes
+        return tot
+
+
+def _split(n: int, parts: int, rank: int, align: int = 1) -> tuple[int, int]:
+    if n % (parts * align):
+        raise ValueError(f"cannot split {n} into {parts} parts aligned to {align}")
+    per = n // parts
+    return rank * per, (rank + 1) * per
+
+
+def load_weights(src: str | GGUFModelFiles, device, layer_range: range | None = None, tp_rank: int = 0, tp_size: int = 1,
+                 first_stage: bool = True, last_stage: bool = True, shard_vocab: bool = True) -> ModelWeights:
+    f = open_gguf(src) if isinstance(src, str) else src
+    cfg = config_from_gguf(f.metadata, f.tensors)
+    layer_range = range(cfg.n_layer) if layer_range is None else layer_range
+    dev = torch.device(device)
+    if cfg.n_head % tp_size or cfg.n_ff % tp_size:
+        raise ValueError(f"tp={tp_size} must divide n_head={cfg.n_head} and n_ff={cfg.n_ff}")
+    # KV heads: shard when possible, otherwise replicate groups (tp > n_head_kv)
+    kv_rep = max(1, tp_size // cfg.n_head_kv)
+    n_kv_local = max(1, cfg.n_head_kv // tp_size)
+    kv_rank = tp_rank // kv_rep
+    hq0, hq1 = _split(cfg.n_head, tp_size, tp_rank)
+    D = cfg.head_dim
+
+    def f32(name):
+        return torch.from_numpy(np.array(f.array(name), dtype=np.float32, copy=True)).to(dev)
+
+    def mat(name, rows=None, cols=None, sub=None) -> DeviceWeight:
+        t = f.tensors[name]
+        raw = f.raw(name)
+        shape = t.shape
+        if sub is not None:  # one expert of a stacked [n_expert, N, K] tensor
+            raw = raw[sub]
+            shape = shape[1:]
+        raw2, shp = slice_raw(raw, t.ggml_type, shape, rows, cols)
+        return DeviceWeight.from_raw(raw2, t.ggml_type, shp, dev)
+
+    layers: dict[int, LayerWeights] = {}
+    for il in layer_range:
+        p = f"blk.{il}."
+        wq = mat(p + "attn_q.weight", rows=(hq0 * D, hq1 * D))
+        wk = mat(p + "attn_k.weight", rows=(kv_rank * n_kv_local * D, (kv_rank + 1) * n_kv_local * D))
+        wv = mat(p + "attn_v.weight", rows=(kv_rank * n_kv_local * D, (kv_rank + 1) * n_kv_local * D))
+        if wq.wtype == wk.wtype == wv.wtype:
+            wqkv = stack_rows([wq, wk, wv])
+        else:  # mixed-type files (Q4_K_M stores attn_v at higher precision): decode the odd ones to fp16
+            dt = [w.to_dense(torch.float16) if w.dense is None else w.dense for w in (wq, wk, wv)]
+            dense = torch.cat([d.float() for d in dt], 0)
+            wqkv = (DeviceWeight(GGMLType.F16, dense.shape[0], dense.shape[1], [], dense) if dev.type == "cpu"
+                    else DeviceWeight(GGMLType.F16, dense.shape[0], dense.shape[1], [dense.to(torch.float16).contiguous()]))
+        lw = LayerWeights(attn_norm=f32(p + "attn_norm.weight"), wqkv=wqkv,
+                          wo=mat(p + "attn_output.weight", cols=(hq0 * D, hq1 * D)), ffn_norm=f32(p + "ffn_norm.weight"))
+        f0, f1 = _split(cfg.n_ff, tp_size, tp_rank, 256 if tp_size > 1 else 1)
+        if cfg.is_moe:
+            lw.router = f32(p + "ffn_gate_inp.weight")
+            for e in range(cfg.n_expert):
+                lw.e_gate.append(mat(p + "ffn_gate_exps.weight", rows=(f0, f1), sub=e))
+                lw.e_up.append(mat(p + "ffn_up_exps.weight", rows=(f0, f1), sub=e))
+                lw.e_down.append(mat(p + "ffn_down_exps.weight", cols=(f0, f1), sub=e))
+        else:
+            lw.w_gate = mat(p + "ffn_gate.weight", rows=(f0, f1))
+            lw.w_up = mat(p + "ffn_up.weight", rows=(f0, f1))
+            lw.w_down = mat(p + "ffn_down.weight", cols=(f0, f1))
+        layers[il] = lw
+
+    tok = mat("token_embd.weight") if first_stage else None
+    out_norm = lm = None
+    v0, v1 = 0, cfg.vocab_size
+    if last_stage:
+        out_norm = f32("output_norm.weight")
+        name = "output.weight" if "output.weight" in f else "token_embd.weight"
+        if shard_vocab and tp_size > 1 and cfg.vocab_size % (2 * tp_size) == 0:
+            v0, v1 = _split(cfg.vocab_size, tp_size, tp_rank)
+        lm = mat(name, rows=(v0, v1))
+    freqs = f32("rope_freqs.weight") if "rope_freqs.weight" in f else None
+    return ModelWeights(cfg, layers, layer_range, tp_rank, tp_size, tok, out_norm, lm, (v0, v1), freqs,
+                        n_head_local=hq1 - hq0, n_head_kv_local=n_kv_local, n_ff_local=cfg.n_ff // tp_size)

@@ -1,0 +1,292 @@
+"""Python-facing ops: thin wrappers over the C ABI for CUDA tensors, PyTorch restatements for CPU tensors.
+
+The CUDA path is the product; the CPU path exists so that engine / scheduling / parallel-layout logic can be
+unit-tested without a GPU (gloo, world_size > 1).  A CUDA tensor never takes the fallback: if the native
+library cannot be loaded the call raises.
+"""
+from __future__ import annotations
+
+import math
+
+import torch
+
+from . import lib as _lib
+from .weights import DeviceWeight
+
+OUT_F16, OUT_F32, OUT_ADD_F32, OUT_SWIGLU_F16 = 0, 1, 2, 3
+_OUT = {"f16": OUT_F16, "f32": OUT_F32, "add": OUT_ADD_F32, "swiglu": OUT_SWIGLU_F16}
+
+# launch counter: every native kernel launch issued through this module (bench.py reports it)
+launch_count = 0
+
+
+def _stream() -> int:
+    return torch.cuda.current_stream().cuda_stream
+
+
+def _p(t: torch.Tensor | None) -> int:
+    return 0 if t is None else t.data_ptr()
+
+
+def _count(n: int = 1):
+    global launch_count
+    launch_count += n
+
+
+def native(t: torch.Tensor) -> bool:
+    return t.is_cuda
+
+
+# ------------------------------------------------------------------------------------------------
+def dequant_rows(w: DeviceWeight, rows: torch.Tensor | None, out_dtype=torch.float32, out: torch.Tensor | None = None):
+    """Decode rows of `w` (all rows when `rows` is None) -> [n, K]; the embedding gather."""
+    n = w.N if rows is None else rows.numel()
+    if w.dense is not None:
+        res = (w.dense if rows is None else w.dense[rows.long()]).to(out_dtype)
+        if out is not None:
+            out.copy_(res)
+            return out
+        return res
+    if out is None:
+        out = torch.empty(n, w.K, dtype=out_dtype, device=w.device)
+    L = _lib.load()
+    fn = L.dlp_dequant_rows_f32 if out.dtype == torch.float32 else L.dlp_dequant_rows_f16
+    if out.dtype not in (torch.float32, torch.float16):
+        raise TypeError("dequant_rows: out dtype must be fp32 or fp16")
+    _lib.check(fn(w.ref(), _p(rows), n, out.data_ptr(), out.stride(0), _stream()), "dequant_rows")
+    _count()
+    return out
+
+
+def rmsnorm(h: torch.Tensor, w: torch.Tensor, eps: float, delta: torch.Tensor | None = None,
+            out: torch.Tensor | None = None) -> torch.Tensor:
+    """h (fp32 [T,E], updated in place with += delta) -> fp16 RMSNorm(h) * w."""
+    T, E = h.shape
+    if out is None:
+        out = torch.empty(T, E, dtype=torch.float16, device=h.device)
+    if not native(h):
+        if delta is not None:
+            h.add_(delta)
+        out.copy_((h * torch.rsqrt(h.pow(2).mean(-1, keepdim=True) + eps) * w).to(torch.float16))
+        return out
+    _lib.check(_lib.load().dlp_rmsnorm(h.data_ptr(), _p(delta), w.data_ptr(), out.data_ptr(), T, E, eps, _stream()), "rmsnorm")
+    _count()
+    return out
+
+
+def _linear_cpu(w, x, w_up, norm_w, eps, out, mode):
+    xf = x.float()
+    if norm_w is not None:
+        xf = (xf * torch.rsqrt(xf.pow(2).mean(-1, keepdim=True) + eps) * norm_w).to(torch.float16).float()
+    y = xf @ w.dense.T
+    if mode == OUT_SWIGLU_F16:
+        y = torch.nn.functional.silu(y) * (xf @ w_up.dense.T)
+    if mode == OUT_ADD_F32:
+        out.add_(y)
+    else:
+        out.copy_(y.to(out.dtype))
+    return out
+
+
+def linear(w: DeviceWeight, x: torch.Tensor, out_mode: str = "f16", w_up: DeviceWeight | None = None,
+           norm_w: torch.Tensor | None = None, eps: float = 0.0, out: torch.Tensor | None = None,
+           scratch: torch.Tensor | None = None) -> torch.Tensor:
+    """y[T,N] (op)= x[T,K] @ W^T with the fused prologue/epilogue options of dlp_gemv / dlp_linear.
+
+    x is fp16, or the fp32 residual stream when `norm_w` (RMSNorm fusion) is given.
+    out_mode: "f16" | "f32" store, "add" (out fp32 += y; residual fusion), "swiglu" (needs w_up)."""
+    mode = _OUT[out_mode]
+    T = x.shape[0]
+    if out is None:
+        if mode == OUT_ADD_F32:
+            raise ValueError("linear: 'add' needs the fp32 destination in `out`")
+        out = torch.empty(T, w.N, dtype=torch.float32 if mode == OUT_F32 else torch.float16, device=x.device)
+    if not native(x):
+        return _linear_cpu(w, x, w_up, norm_w, eps, out, mode)
+    L = _lib.load()
+    up = w_up.ref() if w_up is not None else None
+    if T in (1, 2, 4):
+        _lib.check(L.dlp_gemv(w.ref(), up, x.data_ptr(), _p(norm_w), eps, out.data_ptr(), out.stride(0), mode, T,
+                              _stream()), "gemv")
+        _count()
+        return out
+    if T == 3:  # 2 + 1
+        linear(w, x[:2], out_mode, w_up, norm_w, eps, out[:2])
+        linear(w, x[2:], out_mode, w_up, norm_w, eps, out[2:])
+        return out
+    if norm_w is not None:
+        x = rmsnorm(x, norm_w, eps)
+    elif x.dtype != torch.float16:
+        x = x.to(torch.float16)
+    quant = w.wtype.name.startswith("Q")
+    if quant:
+        need = w.N * w.K * 2 * (2 if w_up is not None else 1)
+        if scratch is None or scratch.numel() * scratch.element_size() < need:
+            scratch = torch.empty(need, dtype=torch.uint8, device=x.device)
+        _count(2 if w_up is not None else 1)
+    sb = 0 if scratch is None else scratch.numel() * scratch.element_size()
+    _lib.check(L.dlp_linear(w.ref(), up, x.data_ptr(), None, 0.0, out.data_ptr(), out.stride(0), mode, T, _p(scratch), sb,
+                            _stream()), "linear")
+    _count()
+    return out
+
+
+def gemm_f16(w: torch.Tensor, x: torch.Tensor, out: torch.Tensor, epilogue: int = 0, w_up: torch.Tensor | None = None,
+             split_k: int = 0) -> torch.Tensor:
+    """Direct access to the tcgen05 GEMM on dense fp16/bf16 tensors (x [T,K], w [N,K])."""
+    T, K = x.shape
+    N = w.shape[0]
+    _lib.check(_lib.load().dlp_gemm_f16(w.data_ptr(), _p(w_up), w.stride(0), x.data_ptr(), x.stride(0), out.data_ptr(),
+                                        out.stride(0), T, N, K, epilogue, int(w.dtype == torch.bfloat16), split_k,
+                                        _stream()), "gemm_f16")
+    _count()
+    return out
+
+
+# ------------------------------------------------------------------------------------------------
+def rope_kv(qkv: torch.Tensor, pos: torch.Tensor, slot: torch.Tensor, inv_freq: torch.Tensor, k_cache: torch.Tensor,
+            v_cache: torch.Tensor, n_head: int, n_head_kv: int, head_dim: int, neox: bool = False,
+            q_out: torch.Tensor | None = None) -> torch.Tensor:
+    """Rotate Q,K; write K,V into the paged cache [pages, Hkv, page, D]; return q (fp16 [T, Hq*D], pre-scaled)."""
+    T = qkv.shape[0]
+    page_size = k_cache.shape[2]
+    n_rot = inv_freq.numel() * 2
+    q_scale = 1.0 / math.sqrt(head_dim)
+    if q_out is None:
+        q_out = torch.empty(T, n_head * head_dim, dtype=torch.float16, device=qkv.device)
+    if not native(qkv):
+        from ..models.reference import apply_rope
+        x = qkv.float().view(T, n_head + 2 * n_head_kv, head_dim)
+        q = apply_rope(x[:, :n_head], pos, inv_freq, neox)
+        k = apply_rope(x[:, n_head:n_head + n_head_kv], pos, inv_freq, neox)
+        v = x[:, n_head + n_head_kv:]
+        q_out.copy_((q * q_scale).reshape(T, -1).to(torch.float16))
+        ok = slot >= 0
+        pg = (slot[ok] // page_size).long()
+        off = (slot[ok] % page_size).long()
+        k_cache[pg, :, off] = k[ok].to(k_cache.dtype)
+        v_cache[pg, :, off] = v[ok].to(v_cache.dtype)
+        return q_out
+    _lib.check(_lib.load().dlp_rope_kv(qkv.data_ptr(), int(qkv.dtype == torch.float16), pos.data_ptr(), slot.data_ptr(),
+                                       inv_freq.data_ptr(), q_out.data_ptr(), k_cache.data_ptr(), v_cache.data_ptr(), T,
+                                       n_head, n_head_kv, head_dim, n_rot, page_size, int(neox), q_scale, _stream()),
+               "rope_kv")
+    _count()
+    return q_out
+
+
+def _attn_cpu(q, k_cache, v_cache, block_table_rows, kv_len, n_head, n_head_kv, head_dim):
+    nq = q.shape[0]
+    page = k_cache.shape[2]
+    out = torch.empty(nq, n_head * head_dim, dtype=torch.float16, device=q.device)
+    g = n_head // n_head_kv
+    for i in range(nq):
+        L = int(kv_len[i])
+        if L == 0:
+            out[i] = 0
+            continue
+        pages = block_table_rows[i][: (L + page - 1) // page].long()
+        K = k_cache[pages].permute(1, 0, 2, 3).reshape(n_head_kv, -1, head_dim)[:, :L].float()
+        V = v_cache[pages].permute(1, 0, 2, 3).reshape(n_head_kv, -1, head_dim)[:, :L].float()
+        qi = q[i].float().view(n_head_kv, g, head_dim)
+        s = torch.einsum("hgd,hld->hgl", qi, K)
+        p = torch.softmax(s, -1)
+        out[i] = torch.einsum("hgl,hld->hgd", p, V).reshape(-1).to(torch.float16)
+    return out
+
+
+def attn_paged(q: torch.Tensor, k_cache: torch.Tensor, v_cache: torch.Tensor, block_table: torch.Tensor,
+               kv_len: torch.Tensor, n_head: int, n_head_kv: int, head_dim: int, bt_row: torch.Tensor | None = None,
+               n_splits: int = 1, workspace: tuple[torch.Tensor, torch.Tensor] | None = None,
+               out: torch.Tensor | None = None) -> torch.Tensor:
+    """Attention of nq independent queries (q fp16 [nq, Hq*D], already scaled) over the paged cache."""
+    nq = q.shape[0]
+    if not native(q):
+        rows = block_table if bt_row is None else block_table[bt_row.long()]
+        res = _attn_cpu(q, k_cache, v_cache, rows, kv_len, n_head, n_head_kv, head_dim)
+        if out is not None:
+            out.copy_(res)
+            return out
+        return res
+    if out is None:
+        out = torch.empty(nq, n_head * head_dim, dtype=torch.float16, device=q.device)
+    po = pm = None
+    if n_splits > 1:
+        if workspace is None:
+            po = torch.empty(nq * n_head * n_splits * head_dim, dtype=torch.float32, device=q.device)
+            pm = torch.empty(nq * n_head * n_splits * 2, dtype=torch.float32, device=q.device)
+        else:
+            po, pm = workspace
+    _lib.check(_lib.load().dlp_attn_paged(q.data_ptr(), k_cache.data_ptr(), v_cache.data_ptr(), block_table.data_ptr(),
+                                          _p(bt_row), kv_len.data_ptr(), out.data_ptr(), _p(po), _p(pm), nq, n_head,
+                                          n_head_kv, head_dim, block_table.shape[1], k_cache.shape[2], n_splits,
+                                          _stream()), "attn_paged")
+    _count(2 if n_splits > 1 else 1)
+    return out
+
+
+def attn_prefill(q: torch.Tensor, k_cache: torch.Tensor, v_cache: torch.Tensor, block_table_row: torch.Tensor, pos0: int,
+                 n_head: int, n_head_kv: int, head_dim: int, out: torch.Tensor | None = None) -> torch.Tensor:
+    """Causal attention of a T-token chunk at positions [pos0, pos0+T) of one sequence."""
+    T = q.shape[0]
+    if not native(q):
+        kv_len = torch.arange(pos0 + 1, pos0 + T + 1, dtype=torch.int32)
+        rows = block_table_row.view(1, -1).expand(T, -1)
+        res = _attn_cpu(q, k_cache, v_cache, rows, kv_len, n_head, n_head_kv, head_dim)
+        if out is not None:
+            out.copy_(res)
+            return out
+        return res
+    if out is None:
+        out = torch.empty(T, n_head * head_dim, dtype=torch.float16, device=q.device)
+    _lib.check(_lib.load().dlp_attn_prefill(q.data_ptr(), k_cache.data_ptr(), v_cache.data_ptr(), block_table_row.data_ptr(),
+                                            out.data_ptr(), T, pos0, n_head, n_head_kv, head_dim, k_cache.shape[2],
+                                            _stream()), "attn_prefill")
+    _count()
+    return out
+
+
+def advance(seq_len: torch.Tensor, pos: torch.Tensor, slot: torch.Tensor, block_table: torch.Tensor, page_size: int):
+    """Device-side: pos = seq_len; slot = lookup(pos); seq_len += 1 (one entry per decoding sequence)."""
+    n = seq_len.numel()
+    if not native(seq_len):
+        pos.copy_(seq_len)
+        pg = (seq_len // page_size).long()
+        ok = pg < block_table.shape[1]
+        pgc = pg.clamp_max(block_table.shape[1] - 1)
+        s = block_table[torch.arange(n), pgc] * page_size + seq_len % page_size
+        slot.copy_(torch.where(ok, s, torch.full_like(s, -1)))
+        seq_len.add_(1)
+        return
+    _lib.check(_lib.load().dlp_advance(seq_len.data_ptr(), pos.data_ptr(), slot.data_ptr(), block_table.data_ptr(),
+                                       block_table.shape[1], page_size, n, _stream()), "advance")
+    _count()
+
+
+def argmax(logits: torch.Tensor, out: torch.Tensor | None = None) -> torch.Tensor:
+    R, V = logits.shape
+    if out is None:
+        out = torch.empty(R, dtype=torch.int32, device=logits.device)
+    if not native(logits):
+        out.copy_(logits.argmax(-1).to(torch.int32))
+        return out
+    _lib.check(_lib.load().dlp_argmax(logits.data_ptr(), R, V, logits.stride(0), out.data_ptr(), _stream()), "argmax")
+    _count()
+    return out
+
+
+def sample(logits: torch.Tensor, top_k: int = 40, top_p: float = 0.95, min_p: float = 0.05, temp: float = 0.8,
+           seed: int = 0, step_ctr: torch.Tensor | None = None, out: torch.Tensor | None = None) -> torch.Tensor:
+    """top-k -> top-p -> min-p -> temperature -> draw (device-side; temp <= 0 is greedy)."""
+    R, V = logits.shape
+    if out is None:
+        out = torch.empty(R, dtype=torch.int32, device=logits.device)
+    if not native(logits):
+        from ..serving.sampler import sample_reference
+        ctr = int(step_ctr[0]) if step_ctr is not None else 0
+        out.copy_(sample_reference(logits, top_k, top_p, min_p, temp, seed + ctr))
+        return out
+    _lib.check(_lib.load().dlp_sample(logits.data_ptr(), R, V, logits.stride(0), top_k, top_p, min_p, temp, seed & 0xFFFFFFFF,
+                                      _p(step_ctr), out.data_ptr(), _stream()), "sample")
+    _count()
+    return out

@@ -1,0 +1,131 @@
+"""Device-resident weight matrices in kernel layout (+ load-time repack of GGUF blocks).
+
+Parity: replaces the reference's buffer-type machinery for weights (`select_weight_buft`,
+`llama.cpp/src/llama-model.cpp:312-323`) and its CPU-side weight repacking (`ggml-cpu/repack.cpp`) with one
+explicit rule per type, documented in `csrc/quant.cuh`: Q8_0 and Q6_K are split into 16-byte-aligned
+structure-of-arrays planes at load; Q4_K / Q5_K super-blocks are already 16-byte multiples and stay native.
+Sharding happens on the raw bytes *before* upload, so each rank only ever touches its own slice of the file.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from dataclasses import dataclass, field
+
+import numpy as np
+import torch
+
+from ..gguf.constants import BLOCK_GEOMETRY, GGMLType
+from ..gguf.quants import dequantize
+from .lib import dlp_weight
+
+KERNEL_TYPES = {GGMLType.F16, GGMLType.BF16, GGMLType.Q8_0, GGMLType.Q4_K, GGMLType.Q5_K, GGMLType.Q6_K}
+
+
+def slice_raw(raw: np.ndarray, ggml_type: GGMLType, shape: tuple[int, int], rows: tuple[int, int] | None = None,
+              cols: tuple[int, int] | None = None) -> tuple[np.ndarray, tuple[int, int]]:
+    """Slice a 2-D weight [N, K] held as raw bytes [N, row_bytes] by output rows and/or (block-aligned) K range."""
+    N, K = shape
+    per, nbytes = BLOCK_GEOMETRY[GGMLType(ggml_type)]
+    raw = raw.reshape(N, K // per * nbytes)
+    if rows is not None:
+        raw = raw[rows[0]:rows[1]]
+        N = rows[1] - rows[0]
+    if cols is not None:
+        k0, k1 = cols
+        if k0 % per or k1 % per:
+            raise ValueError(f"K range {cols} is not aligned to the {per}-element block of {GGMLType(ggml_type).name}")
+        raw = raw[:, k0 // per * nbytes:k1 // per * nbytes]
+        K = k1 - k0
+    return raw, (N, K)
+
+
+@dataclass
+class DeviceWeight:
+    wtype: GGMLType
+    N: int
+    K: int
+    planes: list[torch.Tensor] = field(default_factory=list)  # base, aux0, aux1, aux2 (device memory owners)
+    dense: torch.Tensor | None = None                          # fp32 [N, K] (CPU fallback / oracle only)
+    _c: dlp_weight | None = None
+
+    @property
+    def device(self) -> torch.device:
+        return self.planes[0].device if self.planes else self.dense.device
+
+    @property
+    def nbytes(self) -> int:
+        return sum(p.numel() * p.element_size() for p in self.planes)
+
+    @property
+    def c(self) -> dlp_weight:
+        if self._c is None:
+            ptrs = [p.data_ptr() for p in self.planes] + [0] * (4 - len(self.planes))
+            self._c = dlp_weight(ptrs[0], ptrs[1], ptrs[2], ptrs[3], int(self.wtype), self.N, self.K, 0)
+        return self._c
+
+    def ref(self):
+        return C.byref(self.c)
+
+    def to_dense(self, dtype=torch.float32) -> torch.Tensor:
+        """Decode back to a dense [N, K] tensor (tests / CPU fallback)."""
+        if self.dense is not None:
+            return self.dense.to(dtype)
+        from . import api
+        return api.dequant_rows(self, None, out_dtype=dtype)
+
+    @classmethod
+    def from_raw(cls, raw: np.ndarray, ggml_type: GGMLType, shape: tuple[int, int], device) -> "DeviceWeight":
+        """raw: uint8 [N, row_bytes] in GGUF layout for a logical [N, K] matrix."""
+        t = GGMLType(ggml_type)
+        N, K = shape
+        device = torch.device(device)
+        raw = np.ascontiguousarray(raw).reshape(N, -1)
+        if device.type == "cpu":
+            dense = torch.from_numpy(dequantize(raw, t, (N, K)).astype(np.float32, copy=True))
+            return cls(t if t in KERNEL_TYPES else GGMLType.F16, N, K, [], dense)
+        if t == GGMLType.F32:  # no fp32 matmul path on the device: store as fp16
+            w = torch.from_numpy(raw.view("<f4").reshape(N, K).astype(np.float16)).to(device)
+            return cls(GGMLType.F16, N, K, [w])
+        if t not in KERNEL_TYPES:  # legacy quants (Q4_0, ...) are decoded once at load
+            w = torch.from_numpy(dequantize(raw, t, (N, K)).astype(np.float16)).to(device)
+            return cls(GGMLType.F16, N, K, [w])
+        if K % 256:
+            raise ValueError(f"K={K} must be a multiple of 256 for the device kernels")
+        buf = torch.from_numpy(raw).to(device, non_blocking=False)
+        if t in (GGMLType.F16, GGMLType.BF16):
+            return cls(t, N, K, [buf.view(torch.float16 if t == GGMLType.F16 else torch.bfloat16).view(N, K)])
+        if t in (GGMLType.Q4_K, GGMLType.Q5_K):
+            return cls(t, N, K, [buf])
+        if t == GGMLType.Q8_0:
+            b = buf.view(N, K // 32, 34)
+            d = b[:, :, :2].contiguous().view(torch.float16).view(N, K // 32)
+            qs = b[:, :, 2:].contiguous().view(torch.int8).view(N, K)
+            return cls(t, N, K, [qs, d])
+        if t == GGMLType.Q6_K:
+            b = buf.view(N, K // 256, 210)
+            ql = b[:, :, 0:128].contiguous().view(N, K // 2)
+            qh = b[:, :, 128:192].contiguous().view(N, K // 4)
+            sc = b[:, :, 192:208].contiguous().view(torch.int8).view(N, K // 16)
+            d = b[:, :, 208:210].contiguous().view(torch.float16).view(N, K // 256)
+            return cls(t, N, K, [ql, qh, sc, d])
+        raise NotImplementedError(t)
+
+    @classmethod
+    def from_dense(cls, w: torch.Tensor, ggml_type: GGMLType = GGMLType.F16, device=None) -> "DeviceWeight":
+        """Quantise a dense fp32 [N, K] tensor to `ggml_type` and upload (tests, synthetic models)."""
+        from ..gguf.quants import quantize
+        N, K = w.shape
+        raw = quantize(w.detach().float().cpu().numpy(), ggml_type)
+        return cls.from_raw(raw, ggml_type, (N, K), device or w.device)
+
+
+def stack_rows(weights: list[DeviceWeight]) -> DeviceWeight:
+    """Concatenate matrices with equal K and type along N (e.g. Wq|Wk|Wv -> one fused QKV GEMV)."""
+    w0 = weights[0]
+    if any(w.wtype != w0.wtype or w.K != w0.K for w in weights):
+        raise ValueError("stack_rows: mismatched type or K")
+    N = sum(w.N for w in weights)
+    if w0.dense is not None:
+        return DeviceWeight(w0.wtype, N, w0.K, [], torch.cat([w.dense for w in weights], 0))
+    planes = [torch.cat([w.planes[i] for w in weights], 0) for i in range(len(w0.planes))]
+    return DeviceWeight(w0.wtype, N, w0.K, planes)

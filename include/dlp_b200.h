@@ -1,0 +1,109 @@
+/* dlp_b200 - C ABI of the Blackwell (sm_100a) kernel library behind distributed_llm_pipeline_b200.
+ *
+ * Every entry point returns 0 on success, a positive cudaError_t, or -1 for an argument error;
+ * dlp_last_error() returns a thread-local description.  All work is enqueued on `stream`
+ * (a cudaStream_t passed as void*); nothing here synchronises the device or allocates device memory.
+ * Pointers are device pointers unless stated otherwise.
+ *
+ * Parity notes cite the reference implementation (llama.cpp vendored in un1c4on/Distributed-LLM-Pipeline).
+ */
+#ifndef DLP_B200_H
+#define DLP_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* weight storage types (values mirror GGML type ids) */
+enum { DLP_W_F32 = 0, DLP_W_F16 = 1, DLP_W_Q8_0 = 8, DLP_W_Q4_K = 12, DLP_W_Q5_K = 13, DLP_W_Q6_K = 14, DLP_W_BF16 = 30 };
+
+/* One [N, K] weight matrix in kernel layout (see csrc/quant.cuh):
+ *   F16/BF16: base = dense [N][K];            Q4_K/Q5_K: base = native GGUF super-blocks;
+ *   Q8_0:     base = int8 qs[N][K], aux0 = fp16 d[N][K/32]         (repacked at load);
+ *   Q6_K:     base = ql[N][K/2], aux0 = qh[N][K/4], aux1 = int8 sc[N][K/16], aux2 = fp16 d[N][K/256]. */
+typedef struct dlp_weight {
+    const void* base;
+    const void* aux0;
+    const void* aux1;
+    const void* aux2;
+    int32_t wtype;
+    int32_t N;
+    int32_t K;
+    int32_t reserved;
+} dlp_weight;
+
+/* output modes of dlp_gemv / dlp_linear */
+enum { DLP_OUT_F16 = 0, DLP_OUT_F32 = 1, DLP_OUT_ADD_F32 = 2, DLP_OUT_SWIGLU_F16 = 3 };
+
+const char* dlp_last_error(void);
+int dlp_version(void);
+int dlp_sm_count(void);
+
+/* Decode mat-vec, T in {1,2,4}: y[T,N] (op)= x[T,K] . W^T.  If norm_w != NULL, x is the fp32 residual stream and
+ * RMSNorm(x)*norm_w is fused into the prologue; otherwise x is fp16.  out_mode SWIGLU takes w0=gate, w1=up.
+ * ref: mul_mat_vec_f / mul_mat_vec_q + GLU fusion (ggml-cuda/mmvf.cu, mmvq.cu:143,181-189). */
+int dlp_gemv(const dlp_weight* w0, const dlp_weight* w1, const void* x, const float* norm_w, float eps, void* y,
+             int ldy, int out_mode, int T, void* stream);
+
+/* tcgen05/TMEM/TMA GEMM on dense fp16 (is_bf16=0) or bf16 operands: y[T,N] (op)= x[T,K] . w0[N,K]^T.
+ * epilogue: 0 store f16, 1 store f32, 2 atomic-add f32 (allows split_k>1; 0 = auto), 3 SwiGLU f16 (w1 = up), 4 store bf16.
+ * ref: cuBLAS GemmEx fallback + mma.sync MMQ (ggml-cuda/ggml-cuda.cu:1227-1371, mmq.cuh:3459). */
+int dlp_gemm_f16(const void* w0, const void* w1, int ldw, const void* x, int ldx, void* y, int ldy, int T, int N,
+                 int K, int epilogue, int is_bf16, int split_k, void* stream);
+
+/* Any-T linear layer on any supported weight type.  T<=4 (T in {1,2,4}) routes to dlp_gemv.  Larger T runs the tcgen05
+ * GEMM; block-quantised weights are first decoded to fp16 into `scratch` (needs 2*N*K bytes per matrix, two matrices
+ * for SwiGLU) - the caller owns that buffer.  x must be fp16 when T>4.
+ * ref: ggml_cuda_mul_mat dispatch (ggml-cuda/ggml-cuda.cu:2182-2265) incl. dequantise-then-cuBLAS (:1287-1294). */
+int dlp_linear(const dlp_weight* w0, const dlp_weight* w1, const void* x, const float* norm_w, float eps, void* y,
+               int ldy, int out_mode, int T, void* scratch, size_t scratch_bytes, void* stream);
+
+/* Decode rows of a weight matrix to fp32 / fp16 (row_ids == NULL => rows 0..n_rows-1).  Embedding gather + dequant.
+ * ref: k_get_rows (ggml-cuda/getrows.cu), dequantize_block_* (convert.cu). */
+int dlp_dequant_rows_f32(const dlp_weight* w, const int32_t* row_ids, int n_rows, float* out, int ld_out, void* stream);
+int dlp_dequant_rows_f16(const dlp_weight* w, const int32_t* row_ids, int n_rows, void* out, int ld_out, void* stream);
+
+/* h[T,E] (fp32) += delta (optional, fp32); out (fp16, optional) = RMSNorm(h) * w.   ref: rms_norm_f32 fused mul+add (norm.cu:107). */
+int dlp_rmsnorm(float* h, const float* delta, const float* w, void* out_f16, int T, int E, float eps, void* stream);
+
+/* RoPE on Q,K + paged KV write of K,V.  qkv [T,(Hq+2Hkv)*D] fp32/fp16; q_out fp16 [T,Hq*D] scaled by q_scale;
+ * caches [n_pages][Hkv][page_size][D] fp16; slot[t] = page*page_size+offset (<0: no write).
+ * ref: rope_norm/rope_neox with fused set_rows (rope.cu:44-111,58-78), k_set_rows (set-rows.cu). */
+int dlp_rope_kv(const void* qkv, int qkv_is_f16, const int32_t* pos, const int32_t* slot, const float* inv_freq,
+                void* q_out, void* k_cache, void* v_cache, int T, int Hq, int Hkv, int D, int n_rot, int page_size,
+                int neox, float q_scale, void* stream);
+
+int dlp_swiglu(const void* gate_up, int is_f16, void* out_f16, int T, int F, int ld_in, void* stream);
+
+/* Device-side decode bookkeeping: pos[s]=seq_len[s]; slot[s]=table lookup; seq_len[s]++ . */
+int dlp_advance(int32_t* seq_len, int32_t* pos, int32_t* slot, const int32_t* block_table, int max_pages,
+                int page_size, int n, void* stream);
+
+/* Paged attention for nq queries (decode, batched decode, or one query per prefill token).
+ * q/out fp16 [nq,Hq,D]; kv_len[q] keys visible; bt_row[q] selects the block-table row (NULL: q).
+ * n_splits>1 uses split-KV with workspace part_o [nq*Hq*n_splits*D] / part_ml [nq*Hq*n_splits*2] floats.
+ * ref: flash_attn_ext_vec + flash_attn_combine_results (ggml-cuda/fattn-vec.cuh, fattn-common.cuh:721-772). */
+int dlp_attn_paged(const void* q, const void* k_cache, const void* v_cache, const int32_t* block_table,
+                   const int32_t* bt_row, const int32_t* kv_len, void* out, float* part_o, float* part_ml, int nq,
+                   int Hq, int Hkv, int D, int max_pages, int page_size, int n_splits, void* stream);
+
+/* Causal flash-prefill over the paged cache for one sequence chunk: T query tokens at positions
+ * [pos0, pos0+T) attending to keys [0, pos0+T).  q/out fp16 [T,Hq,D].  ref: flash_attn_ext_f16 (fattn-mma-f16.cuh). */
+int dlp_attn_prefill(const void* q, const void* k_cache, const void* v_cache, const int32_t* block_table_row,
+                     void* out, int T, int pos0, int Hq, int Hkv, int D, int page_size, void* stream);
+
+/* Sampling on device, one row of fp32 logits per output token.  temp<=0 => greedy.
+ * ref: llama_sampler chain top_k/top_p/min_p/temp/dist (llama.cpp/src/llama-sampling.cpp:1348-1918,1255), argmax.cu. */
+int dlp_argmax(const float* logits, int R, int V, int ld, int32_t* out, void* stream);
+int dlp_sample(const float* logits, int R, int V, int ld, int top_k, float top_p, float min_p, float temp,
+               uint32_t seed, const int32_t* step_ctr, int32_t* out, void* stream);
+
+int dlp_f32_to_f16(const float* in, void* out, size_t n, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* DLP_B200_H */

@@ -1,0 +1,32 @@
+import os
+import sys
+
+import pytest
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+
+
+def pytest_configure(config):
+    config.addinivalue_line("markers", "gpu: test needs a CUDA device (B200)")
+
+
+def pytest_collection_modifyitems(config, items):
+    import torch
+    if torch.cuda.is_available():
+        return
+    skip = pytest.mark.skip(reason="no CUDA device")
+    for item in items:
+        if "gpu" in item.keywords:
+            item.add_marker(skip)
+
+
+@pytest.fixture(scope="session")
+def tmp_models(tmp_path_factory):
+    """Tiny random-init GGUF checkpoints shared by the tests."""
+    from distributed_llm_pipeline_b200.gguf import write_synthetic_gguf
+    from distributed_llm_pipeline_b200.models.config import preset
+    root = tmp_path_factory.mktemp("models")
+    out = {}
+    for name, ftype in [("tiny", "F16"), ("tiny", "Q8_0"), ("tiny", "Q4_K_M"), ("tiny128", "F16"), ("tiny-moe", "F16")]:
+        out[(name, ftype)] = write_synthetic_gguf(str(root / f"{name}-{ftype}.gguf"), preset(name), ftype, seed=1)
+    return out

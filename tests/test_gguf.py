@@ -1,0 +1,91 @@
+"""GGUF container + block-quant codecs against gguf-py (the reference's own Python reader / dequantisers)."""
+import numpy as np
+import pytest
+
+from distributed_llm_pipeline_b200.gguf import (GGMLType, GGUFWriter, dequantize, open_gguf, quantize, random_blocks,
+                                                 write_synthetic_gguf)
+from distributed_llm_pipeline_b200.gguf.quants import pack_scale_min_k4, unpack_scale_min_k4
+from distributed_llm_pipeline_b200.models.config import config_from_gguf, preset
+
+gguf = pytest.importorskip("gguf")
+from gguf import quants as GQ  # noqa: E402
+
+TYPES = [(GGMLType.Q8_0, 3e-5), (GGMLType.Q4_0, 1e-2), (GGMLType.Q4_K, 1e-2), (GGMLType.Q5_K, 3e-3), (GGMLType.Q6_K, 1e-3),
+         (GGMLType.F16, 1e-6), (GGMLType.BF16, 1e-4)]
+
+
+@pytest.mark.parametrize("t,tol", TYPES)
+def test_quant_roundtrip_matches_gguf_py(t, tol):
+    rng = np.random.default_rng(0)
+    x = (rng.standard_normal((16, 512)) * 0.05).astype(np.float32)
+    raw = quantize(x, t)
+    mine = dequantize(raw, t, x.shape)
+    ref = GQ.dequantize(raw.reshape(16, -1), gguf.GGMLQuantizationType(int(t)))
+    assert np.array_equal(mine, ref.reshape(x.shape))          # bit-exact decode
+    nmse = ((mine - x) ** 2).sum() / (x ** 2).sum()
+    assert nmse < tol
+
+
+@pytest.mark.parametrize("t", [GGMLType.Q8_0, GGMLType.Q4_K, GGMLType.Q5_K, GGMLType.Q6_K])
+def test_random_blocks_are_valid(t):
+    rng = np.random.default_rng(1)
+    raw = random_blocks(t, 8192, rng)
+    mine = dequantize(raw, t)
+    ref = GQ.dequantize(raw.reshape(1, -1), gguf.GGMLQuantizationType(int(t))).reshape(-1)
+    assert np.array_equal(mine, ref)
+    assert np.isfinite(mine).all() and 0.005 < mine.std() < 0.2
+
+
+def test_scale_min_pack_roundtrip():
+    rng = np.random.default_rng(2)
+    sc = rng.integers(0, 64, (10, 8), dtype=np.uint8)
+    mn = rng.integers(0, 64, (10, 8), dtype=np.uint8)
+    s2, m2 = unpack_scale_min_k4(pack_scale_min_k4(sc, mn))
+    assert np.array_equal(sc, s2) and np.array_equal(mn, m2)
+
+
+@pytest.mark.parametrize("ftype", ["F16", "Q8_0", "Q4_K_M"])
+def test_synthetic_file_readable_by_reference_reader(tmp_path, ftype):
+    cfg = preset("tiny")
+    path = write_synthetic_gguf(str(tmp_path / "m.gguf"), cfg, ftype)
+    mine = open_gguf(path)
+    ref = gguf.GGUFReader(path)
+    assert {t.name for t in ref.tensors} == set(mine.tensors)
+    for t in ref.tensors:
+        a = mine.array(t.name)
+        b = GQ.dequantize(t.data, t.tensor_type).reshape(a.shape)
+        assert np.array_equal(a, b), t.name
+    c2 = config_from_gguf(mine.metadata, mine.tensors)
+    assert (c2.n_embd, c2.n_layer, c2.n_head, c2.n_head_kv, c2.n_ff, c2.vocab_size) == \
+           (cfg.n_embd, cfg.n_layer, cfg.n_head, cfg.n_head_kv, cfg.n_ff, cfg.vocab_size)
+    if ftype == "Q4_K_M":
+        assert mine.tensors["output.weight"].ggml_type == GGMLType.Q6_K
+        assert mine.tensors["blk.0.ffn_gate.weight"].ggml_type == GGMLType.Q4_K
+
+
+def test_writer_kv_types_and_alignment(tmp_path):
+    w = GGUFWriter(str(tmp_path / "kv.gguf"), alignment=64)
+    w.add("general.architecture", "llama")
+    w.add("a.int", 7)
+    w.add("a.float", 0.5)
+    w.add("a.bool", True)
+    w.add("a.strs", ["x", "yz"])
+    w.add("a.arr", np.arange(5, dtype=np.int32))
+    w.add_array("t0", np.arange(64, dtype=np.float32).reshape(2, 32))
+    w.add_array("t1", np.ones((4, 32), np.float32), GGMLType.Q8_0)
+    w.write()
+    f = open_gguf(str(tmp_path / "kv.gguf"))
+    assert f.metadata["a.int"] == 7 and f.metadata["a.bool"] is True and f.metadata["a.strs"] == ["x", "yz"]
+    assert list(f.metadata["a.arr"]) == [0, 1, 2, 3, 4]
+    assert f.files[0].alignment == 64 and f.files[0].data_offset % 64 == 0
+    assert np.array_equal(f.array("t0"), np.arange(64, dtype=np.float32).reshape(2, 32))
+    assert np.allclose(f.array("t1"), 1.0, atol=1e-2)
+
+
+def test_truncated_file_is_rejected(tmp_path):
+    path = write_synthetic_gguf(str(tmp_path / "m.gguf"), preset("tiny"), "F16")
+    data = open(path, "rb").read()
+    bad = tmp_path / "bad.gguf"
+    bad.write_bytes(data[: len(data) // 2])
+    with pytest.raises(ValueError):
+        open_gguf(str(bad))

@@ -1,0 +1,207 @@
+"""Numerics of every CUDA kernel against a plain PyTorch fp32 restatement of the same op.
+
+Metric and thresholds follow the reference's op tests (NMSE; MUL_MAT / FLASH_ATTN_EXT 5e-4:
+llama.cpp/tests/test-backend-ops.cpp:273-287,3716-3718,6049-6051)."""
+import math
+
+import pytest
+import torch
+
+from distributed_llm_pipeline_b200.gguf import GGMLType
+from distributed_llm_pipeline_b200.models.reference import apply_rope, nmse
+from distributed_llm_pipeline_b200.ops import api as ops
+from distributed_llm_pipeline_b200.ops.weights import DeviceWeight
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda"
+WTYPES = [GGMLType.F16, GGMLType.BF16, GGMLType.Q8_0, GGMLType.Q4_K, GGMLType.Q5_K, GGMLType.Q6_K]
+
+
+def _w(N, K, t, seed=0):
+    g = torch.Generator().manual_seed(seed)
+    dense = torch.randn(N, K, generator=g) * 0.05
+    w = DeviceWeight.from_dense(dense, t, DEV)
+    from distributed_llm_pipeline_b200.gguf.quants import dequantize, quantize
+    import numpy as np
+    exact = torch.from_numpy(dequantize(quantize(dense.numpy(), t), t, (N, K)).astype(np.float32)).to(DEV)
+    return w, exact
+
+
+@pytest.mark.parametrize("t", WTYPES)
+def test_dequant_rows_exact(t):
+    w, exact = _w(64, 512, t)
+    out = ops.dequant_rows(w, None)
+    assert torch.equal(out, exact) or nmse(exact, out) < 1e-9
+    rows = torch.tensor([5, 0, 63, 5], dtype=torch.int32, device=DEV)
+    assert nmse(exact[rows.long()], ops.dequant_rows(w, rows)) < 1e-9
+
+
+@pytest.mark.parametrize("t", WTYPES)
+@pytest.mark.parametrize("T", [1, 2, 4])
+def test_gemv_store_and_add(t, T):
+    N, K = 384, 1024
+    w, exact = _w(N, K, t, 1)
+    x = (torch.randn(T, K, device=DEV) * 2).half()
+    ref = x.float() @ exact.T
+    y16 = ops.linear(w, x, "f16")
+    y32 = ops.linear(w, x, "f32")
+    assert nmse(ref, y32) < 5e-6 and nmse(ref, y16) < 5e-6
+    acc = torch.ones(T, N, device=DEV)
+    ops.linear(w, x, "add", out=acc)
+    assert nmse(ref + 1, acc) < 5e-6
+
+
+@pytest.mark.parametrize("t", [GGMLType.F16, GGMLType.Q8_0, GGMLType.Q4_K, GGMLType.Q6_K])
+def test_gemv_fused_norm_and_swiglu(t):
+    N, K, T = 512, 768, 2
+    wg, eg = _w(N, K, t, 2)
+    wu, eu = _w(N, K, t, 3)
+    h = torch.randn(T, K, device=DEV) * 3
+    nw = torch.rand(K, device=DEV) + 0.5
+    eps = 1e-5
+    xn = (h * torch.rsqrt(h.pow(2).mean(-1, keepdim=True) + eps) * nw).half().float()
+    ref = torch.nn.functional.silu(xn @ eg.T) * (xn @ eu.T)
+    y = ops.linear(wg, h, "swiglu", w_up=wu, norm_w=nw, eps=eps)
+    assert nmse(ref, y) < 2e-5
+
+
+@pytest.mark.parametrize("T,N,K", [(5, 128, 64), (16, 256, 256), (37, 384, 1024), (128, 512, 512), (300, 128, 2048), (512, 1024, 4096)])
+@pytest.mark.parametrize("dtype", [torch.float16, torch.bfloat16])
+def test_gemm_tcgen05_store(T, N, K, dtype):
+    w = (torch.randn(N, K, device=DEV) * 0.05).to(dtype)
+    x = torch.randn(T, K, device=DEV).to(dtype)
+    ref = x.float() @ w.float().T
+    y = torch.empty(T, N, device=DEV, dtype=torch.float32)
+    ops.gemm_f16(w, x, y, epilogue=1)
+    assert nmse(ref, y) < 1e-6
+    y16 = torch.empty(T, N, device=DEV, dtype=torch.float16)
+    ops.gemm_f16(w, x, y16, epilogue=0)
+    assert nmse(ref, y16) < 5e-6
+
+
+def test_gemm_tcgen05_ragged_n_splitk_swiglu():
+    T, N, K = 70, 200, 1536   # N not a multiple of 128: OOB rows are zero-filled and masked
+    w = (torch.randn(N, K, device=DEV) * 0.05).half()
+    u = (torch.randn(N, K, device=DEV) * 0.05).half()
+    x = torch.randn(T, K, device=DEV).half()
+    ref = x.float() @ w.float().T
+    acc = torch.full((T, N), 2.0, device=DEV)
+    ops.gemm_f16(w, x, acc, epilogue=2, split_k=4)
+    assert nmse(ref + 2, acc) < 1e-6
+    sw = torch.empty(T, N, device=DEV, dtype=torch.float16)
+    ops.gemm_f16(w, x, sw, epilogue=3, w_up=u)
+    assert nmse(torch.nn.functional.silu(ref) * (x.float() @ u.float().T), sw) < 5e-6
+
+
+@pytest.mark.parametrize("t", [GGMLType.Q8_0, GGMLType.Q4_K, GGMLType.Q6_K])
+def test_linear_quant_gemm_path_uses_scratch(t):
+    T, N, K = 48, 256, 512
+    w, exact = _w(N, K, t, 4)
+    x = torch.randn(T, K, device=DEV).half()
+    scratch = torch.empty(N * K * 2, dtype=torch.uint8, device=DEV)
+    y = ops.linear(w, x, "f32", scratch=scratch)
+    assert nmse(x.float() @ exact.T, y) < 5e-6   # fp16-rounded dequant
+
+
+def test_rmsnorm_with_residual():
+    T, E = 7, 1024
+    h = torch.randn(T, E, device=DEV)
+    d = torch.randn(T, E, device=DEV)
+    w = torch.rand(E, device=DEV) + 0.5
+    ref_h = h + d
+    ref = ref_h * torch.rsqrt(ref_h.pow(2).mean(-1, keepdim=True) + 1e-5) * w
+    out = ops.rmsnorm(h, w, 1e-5, delta=d)
+    assert torch.allclose(h, ref_h, atol=1e-6) and nmse(ref, out) < 1e-6
+
+
+@pytest.mark.parametrize("neox", [False, True])
+@pytest.mark.parametrize("D", [64, 128])
+def test_rope_kv_write(neox, D):
+    T, Hq, Hkv, page = 9, 4, 2, 16
+    qkv = torch.randn(T, (Hq + 2 * Hkv) * D, device=DEV)
+    pos = torch.arange(30, 30 + T, dtype=torch.int32, device=DEV)
+    pages = torch.tensor([3, 1, 2], dtype=torch.int32)
+    slot = (pages[(pos.cpu() // page).long()] * page + pos.cpu() % page).to(torch.int32).to(DEV)
+    inv = (10000.0 ** (-torch.arange(0, D // 2).double() * 2 / D)).float().to(DEV)
+    kc = torch.zeros(4, Hkv, page, D, dtype=torch.float16, device=DEV)
+    vc = torch.zeros_like(kc)
+    q = ops.rope_kv(qkv, pos, slot, inv, kc, vc, Hq, Hkv, D, neox)
+    x = qkv.view(T, Hq + 2 * Hkv, D)
+    q_ref = apply_rope(x[:, :Hq].cpu(), pos.cpu(), inv.cpu(), neox) / math.sqrt(D)
+    k_ref = apply_rope(x[:, Hq:Hq + Hkv].cpu(), pos.cpu(), inv.cpu(), neox)
+    assert nmse(q_ref.reshape(T, -1), q) < 1e-6
+    pg, off = (slot.cpu() // page).long(), (slot.cpu() % page).long()
+    assert nmse(k_ref, kc.cpu()[pg, :, off]) < 1e-6
+    assert nmse(x[:, Hq + Hkv:].cpu(), vc.cpu()[pg, :, off]) < 1e-6
+
+
+def _fill_cache(n_pages, Hkv, page, D, seed=0):
+    g = torch.Generator(device=DEV).manual_seed(seed)
+    kc = torch.randn(n_pages, Hkv, page, D, device=DEV, generator=g).half()
+    vc = torch.randn(n_pages, Hkv, page, D, device=DEV, generator=g).half()
+    return kc, vc
+
+
+@pytest.mark.parametrize("D,Hq,Hkv", [(128, 8, 2), (64, 8, 1), (128, 4, 4), (64, 6, 3)])
+@pytest.mark.parametrize("n_splits", [1, 4])
+def test_attn_paged_decode(D, Hq, Hkv, n_splits):
+    page, n_pages, max_pages = 16, 40, 12
+    kc, vc = _fill_cache(n_pages, Hkv, page, D)
+    lens = torch.tensor([1, 17, 100, 160], dtype=torch.int32, device=DEV)
+    nq = lens.numel()
+    bt = torch.randperm(n_pages)[: nq * max_pages].view(nq, max_pages).to(torch.int32).to(DEV)
+    q = (torch.randn(nq, Hq * D, device=DEV) / math.sqrt(D)).half()
+    out = ops.attn_paged(q, kc, vc, bt, lens, Hq, Hkv, D, n_splits=n_splits)
+    ref = ops._attn_cpu(q.cpu(), kc.cpu(), vc.cpu(), bt.cpu(), lens.cpu(), Hq, Hkv, D)
+    assert nmse(ref, out) < 5e-5
+
+
+@pytest.mark.parametrize("D,Hq,Hkv", [(128, 8, 2), (64, 4, 2)])
+@pytest.mark.parametrize("T,pos0", [(5, 0), (64, 0), (100, 37), (200, 64)])
+def test_attn_prefill_causal(D, Hq, Hkv, T, pos0):
+    page = 16
+    total = pos0 + T
+    n_need = (total + page - 1) // page
+    kc, vc = _fill_cache(n_need + 3, Hkv, page, D, seed=1)
+    row = torch.randperm(n_need + 3)[:n_need].to(torch.int32).to(DEV)
+    q = (torch.randn(T, Hq * D, device=DEV) / math.sqrt(D)).half()
+    out = ops.attn_prefill(q, kc, vc, row, pos0, Hq, Hkv, D)
+    kv_len = torch.arange(pos0 + 1, pos0 + T + 1, dtype=torch.int32)
+    ref = ops._attn_cpu(q.cpu(), kc.cpu(), vc.cpu(), row.cpu().view(1, -1).expand(T, -1), kv_len, Hq, Hkv, D)
+    assert nmse(ref, out) < 5e-4
+
+
+def test_argmax_and_sampler():
+    R, V = 3, 32000
+    lg = torch.randn(R, V, device=DEV)
+    assert torch.equal(ops.argmax(lg).long(), lg.argmax(-1))
+    # greedy through the sampler entry point
+    assert torch.equal(ops.sample(lg, temp=0.0).long(), lg.argmax(-1))
+    # top_k=1 must return the argmax whatever the temperature
+    assert torch.equal(ops.sample(lg, top_k=1, temp=1.5).long(), lg.argmax(-1))
+    # draws stay inside the top-k set and follow the distribution roughly
+    lg2 = torch.full((1, V), -10.0, device=DEV)
+    lg2[0, 7], lg2[0, 99], lg2[0, 1234] = 2.0, 1.0, 0.0
+    ctr = torch.zeros(1, dtype=torch.int32, device=DEV)
+    counts = {7: 0, 99: 0, 1234: 0}
+    for i in range(300):
+        ctr.fill_(i)
+        t = int(ops.sample(lg2, top_k=3, top_p=1.0, min_p=0.0, temp=1.0, seed=5, step_ctr=ctr)[0])
+        assert t in counts
+        counts[t] += 1
+    assert counts[7] > counts[99] > counts[1234] > 0
+    # top-p keeps only the head of the distribution
+    for i in range(50):
+        ctr.fill_(i)
+        assert int(ops.sample(lg2, top_k=40, top_p=0.5, min_p=0.0, temp=1.0, seed=1, step_ctr=ctr)[0]) == 7
+
+
+def test_advance_bookkeeping():
+    page, B, max_pages = 16, 3, 4
+    bt = torch.arange(B * max_pages, dtype=torch.int32, device=DEV).view(B, max_pages)
+    sl = torch.tensor([0, 15, 16], dtype=torch.int32, device=DEV)
+    pos = torch.zeros(B, dtype=torch.int32, device=DEV)
+    slot = torch.zeros(B, dtype=torch.int32, device=DEV)
+    ops.advance(sl, pos, slot, bt, page)
+    assert pos.tolist() == [0, 15, 16] and sl.tolist() == [1, 16, 17]
+    assert slot.tolist() == [0 * 16 + 0, 4 * 16 + 15, 9 * 16 + 0]
