@@ -121,10 +121,10 @@ int dlp_swiglu(const void* gate_up, int is_f16, void* out_f16, int T, int F, int
     return swiglu(gate_up, is_f16, (__half*)out_f16, T, F, ld_in, (cudaStream_t)stream);
 }
 
-int dlp_advance(int32_t* seq_len, int32_t* pos, int32_t* slot, const int32_t* block_table, int max_pages,
-                int page_size, int n, void* stream) {
+int dlp_advance(int32_t* seq_len, const int32_t* active, int32_t* pos, int32_t* slot, int32_t* kv_len,
+                const int32_t* block_table, int max_pages, int page_size, int n, void* stream) {
     DLP_REQUIRE(seq_len && pos && slot && block_table && n > 0, "dlp_advance: bad argument");
-    return advance(seq_len, pos, slot, block_table, max_pages, page_size, n, (cudaStream_t)stream);
+    return advance(seq_len, active, pos, slot, kv_len, block_table, max_pages, page_size, n, (cudaStream_t)stream);
 }
 
 int dlp_attn_paged(const void* q, const void* k_cache, const void* v_cache, const int32_t* block_table,

@@ -194,20 +194,26 @@ int swiglu(const void* gu, int is_f16, __half* out, int T, int F, int ld_in, cud
 }
 
 // ---------------------------------------------------------------------------------------------
-// decode bookkeeping on the device (keeps the per-token loop free of host round trips):
-//   pos[s] = seq_len[s]; slot[s] = block_table[s][pos / page] * page + pos % page; seq_len[s] += 1
-__global__ void advance_kernel(int* __restrict__ seq_len, int* __restrict__ pos, int* __restrict__ slot,
-                               const int* __restrict__ block_table, int max_pages, int page_size, int n) {
+// decode bookkeeping on the device (keeps the per-token loop free of host round trips).  For batch entry s
+// (sequence slot sid = active[s], or s when active == NULL):
+//   pos[s] = seq_len[sid]; slot[s] = block_table[sid][pos / page] * page + pos % page;
+//   kv_len[s] = pos + 1; seq_len[sid] += 1
+__global__ void advance_kernel(int* __restrict__ seq_len, const int* __restrict__ active, int* __restrict__ pos,
+                               int* __restrict__ slot, int* __restrict__ kv_len, const int* __restrict__ block_table,
+                               int max_pages, int page_size, int n) {
     const int s = blockIdx.x * blockDim.x + threadIdx.x;
     if (s >= n) return;
-    const int p = seq_len[s];
+    const int sid = active ? active[s] : s;
+    const int p = seq_len[sid];
     pos[s] = p;
     const int pg = p / page_size;
-    slot[s] = (pg < max_pages) ? block_table[(size_t)s * max_pages + pg] * page_size + p % page_size : -1;
-    seq_len[s] = p + 1;
+    slot[s] = (pg < max_pages) ? block_table[(size_t)sid * max_pages + pg] * page_size + p % page_size : -1;
+    if (kv_len) kv_len[s] = p + 1;
+    seq_len[sid] = p + 1;
 }
-int advance(int* seq_len, int* pos, int* slot, const int* block_table, int max_pages, int page_size, int n, cudaStream_t s) {
-    advance_kernel<<<(n + 127) / 128, 128, 0, s>>>(seq_len, pos, slot, block_table, max_pages, page_size, n);
+int advance(int* seq_len, const int* active, int* pos, int* slot, int* kv_len, const int* block_table, int max_pages,
+            int page_size, int n, cudaStream_t s) {
+    advance_kernel<<<(n + 127) / 128, 128, 0, s>>>(seq_len, active, pos, slot, kv_len, block_table, max_pages, page_size, n);
     DLP_LAUNCH_CHECK();
     return 0;
 }

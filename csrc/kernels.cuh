@@ -40,7 +40,8 @@ int rope_kv(const void* qkv, int qkv_is_f16, const int* pos, const int* slot, co
             __half* kc, __half* vc, int T, int Hq, int Hkv, int D, int n_rot, int page_size, int neox, float q_scale,
             cudaStream_t s);
 int swiglu(const void* gu, int is_f16, __half* out, int T, int F, int ld_in, cudaStream_t s);
-int advance(int* seq_len, int* pos, int* slot, const int* block_table, int max_pages, int page_size, int n, cudaStream_t s);
+int advance(int* seq_len, const int* active, int* pos, int* slot, int* kv_len, const int* block_table, int max_pages,
+            int page_size, int n, cudaStream_t s);
 int argmax(const float* logits, int R, int V, int ld, int* out, cudaStream_t s);
 int sample(const float* logits, int R, int V, int ld, int top_k, float top_p, float min_p, float temp, uint32_t seed,
            const int* step_ctr, int* out, cudaStream_t s);

@@ -121,7 +121,8 @@ class LlamaEngine:
         self.pos = torch.zeros(M, dtype=i32, device=dev)
         self.slot = torch.zeros(M, dtype=i32, device=dev)
         self.kv_len = torch.zeros(M, dtype=i32, device=dev)
-        self.bt_row = torch.zeros(M, dtype=i32, device=dev)
+        self.active = torch.zeros(max_seqs, dtype=i32, device=dev)   # sequence slot of each decode batch row
+        self._active_host: list[int] = []
         self.seq_len_dev = torch.zeros(max_seqs, dtype=i32, device=dev)
         self.next_tok = torch.zeros(max_seqs, dtype=i32, device=dev)
         self.step_ctr = torch.zeros(1, dtype=i32, device=dev)
@@ -228,8 +229,8 @@ class LlamaEngine:
     # ---- attention flavours ---------------------------------------------------------------------
     def _attn_decode(self, il, q, T):
         return ops.attn_paged(q, self.kv.k[il], self.kv.v[il], self.kv.block_table, self.kv_len[:T], self.Hq, self.Hkv,
-                              self.D, bt_row=self.bt_row[:T], n_splits=self.attn_splits if T <= self.max_seqs else 1,
-                              workspace=self.attn_ws if T <= self.max_seqs else None, out=self.att[:T])
+                              self.D, bt_row=self.active[:T], n_splits=self.attn_splits, workspace=self.attn_ws,
+                              out=self.att[:T])
 
     def _attn_prefill_for(self, sid: int, pos0: int):
         def fn(il, q, T):
@@ -291,9 +292,8 @@ class LlamaEngine:
 
     # ---- public: decode -------------------------------------------------------------------------
     def _decode_body(self, B: int, sample: bool):
-        """One decode step for the sequences in slots bt_row[:B]; everything stays on the device."""
-        ops.advance(self._seq_len_view, self.pos[:B], self.slot[:B], self._bt_view, self.page_size)
-        self.kv_len[:B].copy_(self._seq_len_view)  # after advance: length including the new token
+        """One decode step for the sequence slots listed in self.active[:B]; everything stays on the device."""
+        ops.advance(self.seq_len_dev, self.active, self.pos, self.slot, self.kv_len, self.kv.block_table, self.page_size, B)
         if self.first_stage:
             self._embed(B, self.next_tok[:B])  # input ids = previously sampled (or host-provided) tokens
         self._run_layers(B, self._attn_decode)
@@ -307,40 +307,29 @@ class LlamaEngine:
     @torch.no_grad()
     def decode(self, sids: list[int], tokens=None, hidden_in: torch.Tensor | None = None, sample: bool = True,
                use_graph: bool = True):
-        """One token for each sequence in `sids` (which must occupy slots 0..B-1 for the graph path).
+        """One token for each sequence in `sids` (any subset of slots; batch row i belongs to sids[i]).
         tokens: host ints / tensor, or None to feed back the previously sampled tokens (device resident).
         Returns next-token ids (device int32 [B]) when sampling, else logits [B, vocab]; or hidden states."""
         B = len(sids)
         for sid in sids:
             seq = self.seqs[sid]
             self.kv.ensure(seq, seq.length + 1)
-        contiguous = sids == list(range(B))
-        if contiguous:
-            self._seq_len_view, self._bt_view = self.seq_len_dev[:B], self.kv.block_table[:B]
-            if not getattr(self, "_bt_row_iota", 0) >= B:
-                self.bt_row[:self.max_seqs].copy_(torch.arange(self.max_seqs, dtype=torch.int32))
-                self._bt_row_iota = self.max_seqs
-        else:
-            idx = torch.tensor(sids, dtype=torch.long, device=self.device)
-            self._seq_len_view, self._bt_view = self.seq_len_dev[idx], self.kv.block_table[idx].contiguous()
-            self.bt_row[:B].copy_(torch.arange(B, dtype=torch.int32))
-            self._bt_row_iota = 0
+        if sids != self._active_host:
+            self.active[:B].copy_(torch.tensor(sids, dtype=torch.int32), non_blocking=False)
+            self._active_host = list(sids)
         if tokens is not None and self.first_stage:
             self.next_tok[:B].copy_(torch.as_tensor(tokens, dtype=torch.int32), non_blocking=True)
         if hidden_in is not None:
             self.h[:B].copy_(hidden_in)
-        graphable = (use_graph and contiguous and self.device.type == "cuda" and not self.cfg.is_moe
+        graphable = (use_graph and self.device.type == "cuda" and not self.cfg.is_moe
                      and not getattr(self.comm, "no_graph", False))
         if graphable:
-            key = (B, sample)
-            g = self._graphs.get(key)
+            g = self._graphs.get((B, sample))
             if g is None:
                 g = self._capture(B, sample)
             g.replay()
         else:
             self._decode_body(B, sample)
-            if not contiguous:
-                self.seq_len_dev[idx] = self._seq_len_view
         for sid in sids:
             self.seqs[sid].length += 1
         if not self.last_stage:
@@ -385,7 +374,7 @@ class LlamaEngine:
         for _ in range(n_predict - 1):
             if out[-1] in stop_ids:
                 break
-            nt = self.decode([sid], use_graph=(sid == 0))
+            nt = self.decode([sid])
             out.append(int(nt[0]))
         if own:
             self.free_seq(sid)

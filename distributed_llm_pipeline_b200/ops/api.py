@@ -246,20 +246,24 @@ def attn_prefill(q: torch.Tensor, k_cache: torch.Tensor, v_cache: torch.Tensor, 
     return out
 
 
-def advance(seq_len: torch.Tensor, pos: torch.Tensor, slot: torch.Tensor, block_table: torch.Tensor, page_size: int):
-    """Device-side: pos = seq_len; slot = lookup(pos); seq_len += 1 (one entry per decoding sequence)."""
-    n = seq_len.numel()
+def advance(seq_len: torch.Tensor, active: torch.Tensor | None, pos: torch.Tensor, slot: torch.Tensor,
+            kv_len: torch.Tensor | None, block_table: torch.Tensor, page_size: int, n: int):
+    """Device-side bookkeeping for the n batch entries whose sequence slots are active[:n] (see dlp_advance)."""
     if not native(seq_len):
-        pos.copy_(seq_len)
-        pg = (seq_len // page_size).long()
+        sid = (active[:n] if active is not None else torch.arange(n)).long()
+        p = seq_len[sid]
+        pos[:n].copy_(p)
+        pg = (p // page_size).long()
         ok = pg < block_table.shape[1]
         pgc = pg.clamp_max(block_table.shape[1] - 1)
-        s = block_table[torch.arange(n), pgc] * page_size + seq_len % page_size
-        slot.copy_(torch.where(ok, s, torch.full_like(s, -1)))
-        seq_len.add_(1)
+        s = block_table[sid, pgc] * page_size + p % page_size
+        slot[:n].copy_(torch.where(ok, s, torch.full_like(s, -1)))
+        if kv_len is not None:
+            kv_len[:n].copy_(p + 1)
+        seq_len[sid] = p + 1
         return
-    _lib.check(_lib.load().dlp_advance(seq_len.data_ptr(), pos.data_ptr(), slot.data_ptr(), block_table.data_ptr(),
-                                       block_table.shape[1], page_size, n, _stream()), "advance")
+    _lib.check(_lib.load().dlp_advance(seq_len.data_ptr(), _p(active), pos.data_ptr(), slot.data_ptr(), _p(kv_len),
+                                       block_table.data_ptr(), block_table.shape[1], page_size, n, _stream()), "advance")
     _count()
 
 

@@ -78,9 +78,11 @@ int dlp_rope_kv(const void* qkv, int qkv_is_f16, const int32_t* pos, const int32
 
 int dlp_swiglu(const void* gate_up, int is_f16, void* out_f16, int T, int F, int ld_in, void* stream);
 
-/* Device-side decode bookkeeping: pos[s]=seq_len[s]; slot[s]=table lookup; seq_len[s]++ . */
-int dlp_advance(int32_t* seq_len, int32_t* pos, int32_t* slot, const int32_t* block_table, int max_pages,
-                int page_size, int n, void* stream);
+/* Device-side decode bookkeeping for batch entries s < n, sequence slot sid = active[s] (active NULL: sid = s):
+ * pos[s]=seq_len[sid]; slot[s]=block-table lookup; kv_len[s]=pos+1 (optional); seq_len[sid]++ .
+ * ref: llama_kv_cache::find_slot + set_input_k_idxs on the host (llama-kv-cache.cpp:696,1240). */
+int dlp_advance(int32_t* seq_len, const int32_t* active, int32_t* pos, int32_t* slot, int32_t* kv_len,
+                const int32_t* block_table, int max_pages, int page_size, int n, void* stream);
 
 /* Paged attention for nq queries (decode, batched decode, or one query per prefill token).
  * q/out fp16 [nq,Hq,D]; kv_len[q] keys visible; bt_row[q] selects the block-table row (NULL: q).

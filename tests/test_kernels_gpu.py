@@ -145,7 +145,7 @@ def _fill_cache(n_pages, Hkv, page, D, seed=0):
 @pytest.mark.parametrize("D,Hq,Hkv", [(128, 8, 2), (64, 8, 1), (128, 4, 4), (64, 6, 3)])
 @pytest.mark.parametrize("n_splits", [1, 4])
 def test_attn_paged_decode(D, Hq, Hkv, n_splits):
-    page, n_pages, max_pages = 16, 40, 12
+    page, n_pages, max_pages = 16, 64, 12
     kc, vc = _fill_cache(n_pages, Hkv, page, D)
     lens = torch.tensor([1, 17, 100, 160], dtype=torch.int32, device=DEV)
     nq = lens.numel()
@@ -202,6 +202,8 @@ def test_advance_bookkeeping():
     sl = torch.tensor([0, 15, 16], dtype=torch.int32, device=DEV)
     pos = torch.zeros(B, dtype=torch.int32, device=DEV)
     slot = torch.zeros(B, dtype=torch.int32, device=DEV)
-    ops.advance(sl, pos, slot, bt, page)
+    kvl = torch.zeros(B, dtype=torch.int32, device=DEV)
+    ops.advance(sl, None, pos, slot, kvl, bt, page, B)
+    assert kvl.tolist() == [1, 16, 17]
     assert pos.tolist() == [0, 15, 16] and sl.tolist() == [1, 16, 17]
     assert slot.tolist() == [0 * 16 + 0, 4 * 16 + 15, 9 * 16 + 0]
