@@ -381,3 +381,52 @@ int attn_prefill(const __half* q, const __half* kc, const __half* vc, const int*
 }
 
 }  // namespace dlp
+
+// =================================================================================================
+// Split-KV paged attention without a caller-provided workspace.
+//
+// Some hosts of this library are not in a position to hand us scratch memory: a serving process that carved
+// the whole HBM into weights + KV pages at start-up and then froze its allocator, a plug-in running under a
+// "no device allocation after init" rule, or code sitting between cudaStreamBeginCapture / EndCapture where
+// cudaMalloc is illegal.  For them the split-KV partial results (the only scratch `attn_paged` needs) live in
+// a fixed array inside this module's device image.  Costs and rules, all of which the header repeats:
+//   * the array is ATTN_STATIC_SCRATCH_FLOATS floats (4 MiB) on every GPU that loads the library, until exit;
+//   * a launch needs nq * Hq * n_splits * (D + 2) floats and is refused with an error beyond that;
+//   * every call on a device shares the same array, so calls that overlap on the GPU (different streams, or
+//     graphs replayed concurrently) race - serialise them;
+//   * nothing has to start at zero: the partial kernel writes every (query, head, split) slot - empty splits
+//     write m = -inf, l = 0 - before the combine kernel reads it, so stale contents of an earlier call are
+//     never observed.
+// In host code the array's name is only a handle: the device address is obtained once per device with
+// cudaGetSymbolAddress (device current, return code checked) on the first call there, which therefore must
+// happen outside stream capture.
+namespace dlp {
+
+constexpr size_t ATTN_STATIC_SCRATCH_FLOATS = size_t(1) << 20;  // keep in sync with DLP_ATTN_STATIC_SCRATCH_FLOATS
+static __device__ __align__(256) float g_attn_static_scratch[ATTN_STATIC_SCRATCH_FLOATS];
+
+int attn_paged_static(AttnParams p, int D, cudaStream_t s) {
+    DLP_REQUIRE(p.nq > 0 && p.Hq > 0 && p.n_splits >= 1 && D > 0, "attn_paged_static: bad shape");
+    const size_t n_part = (size_t)p.nq * p.Hq * p.n_splits;
+    const size_t need = p.n_splits > 1 ? n_part * (size_t)(D + 2) : 0;
+    DLP_REQUIRE(need <= ATTN_STATIC_SCRATCH_FLOATS,
+                "attn_paged_static: nq*Hq*n_splits*(D+2) = %zu floats exceeds the built-in scratch of %zu floats; "
+                "lower n_splits / batch or use dlp_attn_paged with your own workspace",
+                need, (size_t)ATTN_STATIC_SCRATCH_FLOATS);
+    constexpr int MAX_DEV = 64;
+    static float* dev_ptr[MAX_DEV] = {nullptr};
+    int dev = -1;
+    DLP_CHECK_CUDA(cudaGetDevice(&dev));
+    DLP_REQUIRE(dev >= 0 && dev < MAX_DEV, "attn_paged_static: device ordinal %d out of range", dev);
+    float* ptr = dev_ptr[dev];
+    if (ptr == nullptr) {  // once per device, with that device current (racing first calls store the same value)
+        DLP_CHECK_CUDA(cudaGetSymbolAddress((void**)&ptr, g_attn_static_scratch));
+        DLP_REQUIRE(ptr != nullptr, "attn_paged_static: cudaGetSymbolAddress returned a null address");
+        dev_ptr[dev] = ptr;
+    }
+    p.part_o = ptr;                      // [nq, Hq, n_splits, D]
+    p.part_ml = ptr + n_part * (size_t)D;  // [nq, Hq, n_splits, 2]
+    return attn_paged(p, D, s);
+}
+
+}  // namespace dlp

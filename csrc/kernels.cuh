@@ -47,6 +47,7 @@ int sample(const float* logits, int R, int V, int ld, int top_k, float top_p, fl
            const int* step_ctr, int* out, cudaStream_t s);
 int f32_to_f16(const float* in, __half* out, size_t n, cudaStream_t s);
 int attn_paged(const AttnParams& p, int D, cudaStream_t s);
+int attn_paged_static(AttnParams p, int D, cudaStream_t s);
 int attn_prefill(const __half* q, const __half* kc, const __half* vc, const int* bt_row, __half* out, int T, int pos0,
                  int Hq, int Hkv, int D, int page_size, cudaStream_t s);
 

@@ -92,6 +92,25 @@ int dlp_attn_paged(const void* q, const void* k_cache, const void* v_cache, cons
                    const int32_t* bt_row, const int32_t* kv_len, void* out, float* part_o, float* part_ml, int nq,
                    int Hq, int Hkv, int D, int max_pages, int page_size, int n_splits, void* stream);
 
+/* dlp_attn_paged for callers that cannot supply the split-KV workspace.  (No counterpart in the reference: it always
+ * allocates its own split buffers from the backend pool.)
+ * Who needs it: hosts that are not allowed to allocate device memory when they call us - a server that split all of HBM
+ * into weights and KV pages at start-up and froze its allocator, a plug-in under a "no allocation after init" rule, or
+ * code running inside a stream capture, where cudaMalloc is illegal.  Inputs and outputs are still the caller's.
+ * How: the partial results live in a fixed array compiled into the library's device image,
+ * DLP_ATTN_STATIC_SCRATCH_FLOATS floats (4 MiB) that every GPU loading the library holds until the process exits.
+ * Limit: nq*Hq*n_splits*(D+2) must not exceed DLP_ATTN_STATIC_SCRATCH_FLOATS, otherwise the call returns -1 and
+ * dlp_last_error() says by how much (n_splits == 1 needs no scratch at all).
+ * Rules: (1) the first call on each device looks the array's device address up (cudaGetSymbolAddress) - make that first
+ * call outside any stream capture; (2) all calls on a device share the one array, so two calls whose kernels can overlap
+ * on the GPU (different streams, concurrently replayed graphs) race: order them yourself; (3) nothing needs clearing
+ * between calls - every slot the combine step reads is rewritten by the same call first, so leftovers are never seen.
+ * The call itself performs no cudaMalloc/cudaFree and uses no allocating library routine. */
+#define DLP_ATTN_STATIC_SCRATCH_FLOATS (1u << 20)
+int dlp_attn_paged_static(const void* q, const void* k_cache, const void* v_cache, const int32_t* block_table,
+                          const int32_t* bt_row, const int32_t* kv_len, void* out, int nq, int Hq, int Hkv, int D,
+                          int max_pages, int page_size, int n_splits, void* stream);
+
 /* Causal flash-prefill over the paged cache for one sequence chunk: T query tokens at positions
  * [pos0, pos0+T) attending to keys [0, pos0+T).  q/out fp16 [T,Hq,D].  ref: flash_attn_ext_f16 (fattn-mma-f16.cuh). */
 int dlp_attn_prefill(const void* q, const void* k_cache, const void* v_cache, const int32_t* block_table_row,
