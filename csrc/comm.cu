@@ -1,0 +1,93 @@
+// Symmetric (peer-mapped) device memory + the stand-alone pieces of the fused tensor-parallel all-reduce.
+//
+// The reference's tensor parallelism moves every activation through one hub GPU with cudaMemcpyPeerAsync
+// (llama.cpp/ggml/src/ggml-cuda/ggml-cuda.cu:1680-1744) and has no reduction at all.  Here every rank owns
+// a "reduce buffer" that all peers map through CUDA IPC; the row-parallel mat-vec kernels push their partial
+// rows straight into the peers' buffers over NVLink (gemv.cu, GV_PUSH_F32) and the next kernel's prologue
+// sums them (ArIn).  This file provides the allocation / handle exchange primitives, the epoch counter bump
+// and a stand-alone consumer for places where no mat-vec follows (pipeline-stage boundary).
+#include "kernels.cuh"
+
+namespace dlp {
+
+__global__ void bump_kernel(int* ctr) { *ctr += 1; }
+
+__global__ void __launch_bounds__(256) ar_consume_kernel(const float* __restrict__ h_in, float* __restrict__ h_out, const ArIn a, int K, int T) {
+    if ((int)threadIdx.x < a.tp) {
+        const uint32_t want = (uint32_t)*a.epoch;
+        const long long t0 = clock64();
+        uint32_t v;
+        do {
+            asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(a.flags + threadIdx.x) : "memory");
+            if (clock64() - t0 > (1ll << 32)) { if (a.error) atomicExch(a.error, 1); break; }
+        } while ((int32_t)(v - want) < 0);
+    }
+    __syncthreads();
+    const int t = blockIdx.x;
+    for (int k = threadIdx.x * 4; k < K; k += blockDim.x * 4) {
+        float4 v = *reinterpret_cast<const float4*>(h_in + (size_t)t * K + k);
+        for (int r = 0; r < a.tp; ++r) {
+            const float4 d = __ldcg(reinterpret_cast<const float4*>(a.buf + ((size_t)r * T + t) * K + k));
+            v.x += d.x; v.y += d.y; v.z += d.z; v.w += d.w;
+        }
+        *reinterpret_cast<float4*>(h_out + (size_t)t * K + k) = v;
+    }
+}
+
+int ar_consume(const float* h_in, float* h_out, const ArIn& a, int K, int T, cudaStream_t s) {
+    DLP_REQUIRE(a.buf && a.flags && a.epoch && a.tp >= 1 && a.tp <= 8, "ar_consume: bad descriptor");
+    ar_consume_kernel<<<T, 256, 0, s>>>(h_in, h_out, a, K, T);
+    DLP_LAUNCH_CHECK();
+    return 0;
+}
+
+int bump(int* ctr, cudaStream_t s) {
+    bump_kernel<<<1, 1, 0, s>>>(ctr);
+    DLP_LAUNCH_CHECK();
+    return 0;
+}
+
+}  // namespace dlp
+
+using namespace dlp;
+
+extern "C" {
+
+int dlp_symm_alloc(size_t bytes, void** ptr) {
+    DLP_REQUIRE(ptr && bytes > 0, "dlp_symm_alloc: bad argument");
+    DLP_CHECK_CUDA(cudaMalloc(ptr, bytes));
+    DLP_CHECK_CUDA(cudaMemset(*ptr, 0, bytes));
+    DLP_CHECK_CUDA(cudaDeviceSynchronize());
+    return 0;
+}
+int dlp_symm_free(void* ptr) {
+    DLP_CHECK_CUDA(cudaFree(ptr));
+    return 0;
+}
+int dlp_ipc_export(void* ptr, void* handle64) {
+    DLP_REQUIRE(ptr && handle64, "dlp_ipc_export: null argument");
+    static_assert(sizeof(cudaIpcMemHandle_t) == 64, "unexpected IPC handle size");
+    DLP_CHECK_CUDA(cudaIpcGetMemHandle(reinterpret_cast<cudaIpcMemHandle_t*>(handle64), ptr));
+    return 0;
+}
+int dlp_ipc_import(const void* handle64, void** ptr) {
+    DLP_REQUIRE(ptr && handle64, "dlp_ipc_import: null argument");
+    cudaIpcMemHandle_t h;
+    memcpy(&h, handle64, sizeof(h));
+    DLP_CHECK_CUDA(cudaIpcOpenMemHandle(ptr, h, cudaIpcMemLazyEnablePeerAccess));
+    return 0;
+}
+int dlp_ipc_close(void* ptr) {
+    DLP_CHECK_CUDA(cudaIpcCloseMemHandle(ptr));
+    return 0;
+}
+int dlp_bump(int32_t* ctr, void* stream) {
+    DLP_REQUIRE(ctr, "dlp_bump: null argument");
+    return bump(ctr, (cudaStream_t)stream);
+}
+int dlp_memcpy_d2h(void* dst, const void* src, size_t bytes) {
+    DLP_CHECK_CUDA(cudaMemcpy(dst, src, bytes, cudaMemcpyDeviceToHost));
+    return 0;
+}
+
+}  // extern "C"

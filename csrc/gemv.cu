@@ -12,6 +12,33 @@ namespace dlp {
 
 __device__ __forceinline__ float gv_silu(float x) { return x / (1.f + __expf(-x)); }
 
+// ---- fused all-reduce, consumer side -------------------------------------------------------------
+// Row-parallel partial results of the previous GEMV arrive in this rank's `ar_in.buf` ([tp][T][K] fp32), pushed
+// by every peer (and by ourselves) over NVLink together with a per-peer epoch flag.  The consumer waits for
+// the tp flags, then forms  h_out = h_in + sum_p buf[p]  in rank order (bitwise identical on every rank).
+__device__ __forceinline__ uint32_t ld_acquire_sys_u32(const uint32_t* p) {
+    uint32_t v;
+    asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ void st_release_sys_u32(uint32_t* p, uint32_t v) {
+    asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+
+__device__ __forceinline__ void ar_wait(const ArIn& a) {
+    if ((int)threadIdx.x < a.tp) {
+        const uint32_t want = (uint32_t)*a.epoch;
+        const long long t0 = clock64();
+        while ((int32_t)(ld_acquire_sys_u32(a.flags + threadIdx.x) - want) < 0) {
+            if (clock64() - t0 > (1ll << 32)) {  // ~2 s: a peer died or diverged; record and fall through
+                if (a.error) atomicExch(a.error, 1);
+                break;
+            }
+        }
+    }
+    __syncthreads();
+}
+
 template <int NT>
 __device__ __forceinline__ void stage_x(const GemvParams& p, int K, __half* xs, float* red) {
     // xs[t][k] <- fp16 activations (optionally RMS-normalised from the fp32 residual stream)
@@ -25,17 +52,29 @@ __device__ __forceinline__ void stage_x(const GemvParams& p, int K, __half* xs, 
         return;
     }
     const float* h = reinterpret_cast<const float*>(p.x);
+    const bool ar = p.ar_in.buf != nullptr;
+    if (ar) ar_wait(p.ar_in);
+    float* hs = reinterpret_cast<float*>(xs + (size_t)NT * K);  // fp32 staging of the reduced row (AR only)
 #pragma unroll
     for (int t = 0; t < NT; ++t) {
         float ss = 0.f;
         for (int k = tid * 4; k < K; k += nth * 4) {
-            const float4 v = *reinterpret_cast<const float4*>(h + (size_t)t * K + k);
+            float4 v = *reinterpret_cast<const float4*>(h + (size_t)t * K + k);
+            if (ar) {
+                for (int r = 0; r < p.ar_in.tp; ++r) {
+                    const float4 d = __ldcg(reinterpret_cast<const float4*>(p.ar_in.buf + ((size_t)r * NT + t) * K + k));
+                    v.x += d.x; v.y += d.y; v.z += d.z; v.w += d.w;
+                }
+                *reinterpret_cast<float4*>(hs + k) = v;
+                if (blockIdx.x == 0) *reinterpret_cast<float4*>(p.ar_in.h_out + (size_t)t * K + k) = v;
+            }
             ss += v.x * v.x + v.y * v.y + v.z * v.z + v.w * v.w;
         }
         ss = block_sum(ss, red);
         const float rs = rsqrtf(ss / (float)K + p.eps);
         for (int k = tid * 4; k < K; k += nth * 4) {
-            const float4 v = *reinterpret_cast<const float4*>(h + (size_t)t * K + k);
+            const float4 v = ar ? *reinterpret_cast<const float4*>(hs + k)
+                                : *reinterpret_cast<const float4*>(h + (size_t)t * K + k);
             const float4 g = *reinterpret_cast<const float4*>(p.norm_w + k);
             __half2 a = __floats2half2_rn(v.x * rs * g.x, v.y * rs * g.y);
             __half2 b = __floats2half2_rn(v.z * rs * g.z, v.w * rs * g.w);
@@ -44,8 +83,26 @@ __device__ __forceinline__ void stage_x(const GemvParams& p, int K, __half* xs, 
             o.y = *reinterpret_cast<uint32_t*>(&b);
             *reinterpret_cast<uint2*>(xs + (size_t)t * K + k) = o;
         }
+        __syncthreads();  // hs is reused by the next token
     }
     __syncthreads();
+}
+
+// ---- fused all-reduce, producer side ----------------------------------------------------------------
+// After a CTA has pushed all its rows, thread 0 fences at system scope and bumps a local counter; the CTA that
+// observes the final count publishes this rank's epoch flag to every peer (release at system scope).
+__device__ __forceinline__ void ar_signal(const ArOut& a) {
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        __threadfence_system();
+        const unsigned prev = atomicAdd(a.done_counter, 1u);
+        if (prev == gridDim.x - 1) {
+            *a.done_counter = 0;  // ready for the next launch that uses this counter
+            __threadfence_system();
+            const uint32_t e = (uint32_t)*a.epoch;
+            for (int pr = 0; pr < a.tp; ++pr) st_release_sys_u32(a.peer_flags[pr] + a.rank, e);
+        }
+    }
 }
 
 template <int NT>
@@ -67,7 +124,11 @@ __device__ __forceinline__ void gv_write(const GemvParams& p, int row, float (&a
         for (int tt = 0; tt < NT; ++tt) if (tt == t) v = s ? acc[1][tt] : acc[0][tt];
         const size_t o = (size_t)t * p.ldy + row + s;
         if (row + s < p.w0.N) {
-            if (p.out_mode == GV_STORE_F16) reinterpret_cast<__half*>(p.y)[o] = __float2half_rn(v);
+            if (p.out_mode == GV_PUSH_F32) {
+                // partial sum of this rank's K shard -> slot [rank][t][row] of every peer's reduce buffer
+                for (int pr = 0; pr < p.ar_out.tp; ++pr)
+                    p.ar_out.peer_buf[pr][((size_t)p.ar_out.rank * NT + t) * p.w0.N + row + s] = v;
+            } else if (p.out_mode == GV_STORE_F16) reinterpret_cast<__half*>(p.y)[o] = __float2half_rn(v);
             else if (p.out_mode == GV_STORE_F32) reinterpret_cast<float*>(p.y)[o] = v;
             else reinterpret_cast<float*>(p.y)[o] += v;  // GV_ADD_F32: each output has exactly one writer
         }
@@ -137,6 +198,7 @@ __global__ void __launch_bounds__(256) gemv_dense_kernel(const GemvParams p) {
             for (int t = 0; t < NT; ++t) acc[s][t] = warp_sum(acc[s][t]);
         gv_write<NT>(p, row, acc, dual, lane);
     }
+    if (p.out_mode == GV_PUSH_F32) ar_signal(p.ar_out);
 }
 
 // ---- block-quantised weights ---------------------------------------------------------------------
@@ -145,7 +207,8 @@ __global__ void __launch_bounds__(256) gemv_quant_kernel(const GemvParams p) {
     extern __shared__ __align__(16) uint8_t gv_smem[];
     const int K = p.w0.K, N = p.w0.N;
     __half* xs = reinterpret_cast<__half*>(gv_smem);
-    float* xsum = reinterpret_cast<float*>(gv_smem + (size_t)NT * K * 2);  // [NT][K/16] sums of x per 16 elements
+    // [NT][K/16] sums of x per 16 elements (placed after the optional fp32 AR staging row)
+    float* xsum = reinterpret_cast<float*>(gv_smem + (size_t)NT * K * 2 + (p.ar_in.buf ? (size_t)K * 4 : 0));
     __shared__ float red[32];
     stage_x<NT>(p, K, xs, red);
     constexpr bool HAS_BIAS = (WT == W_Q4_K || WT == W_Q5_K);
@@ -209,6 +272,7 @@ __global__ void __launch_bounds__(256) gemv_quant_kernel(const GemvParams p) {
             for (int t = 0; t < NT; ++t) acc[s][t] = warp_sum(acc[s][t]);
         gv_write<NT>(p, row, acc, dual, lane);
     }
+    if (p.out_mode == GV_PUSH_F32) ar_signal(p.ar_out);
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -238,7 +302,9 @@ int gemv(const GemvParams& p, int wtype, cudaStream_t stream) {
     DLP_REQUIRE(K % 256 == 0, "gemv: K=%d must be a multiple of 256", K);
     DLP_REQUIRE(N % 2 == 0, "gemv: N=%d must be even", N);
     DLP_REQUIRE(p.out_mode != GV_SWIGLU_F16 || p.w1.base != nullptr, "gemv: SwiGLU needs both gate and up weights");
-    size_t smem = (size_t)T * K * 2;
+    size_t smem = (size_t)T * K * 2 + (p.ar_in.buf ? (size_t)K * 4 : 0);
+    DLP_REQUIRE(p.ar_in.buf == nullptr || p.norm_w != nullptr, "gemv: the fused all-reduce prologue needs the RMSNorm fusion");
+    DLP_REQUIRE(p.out_mode != GV_PUSH_F32 || (p.ar_out.tp >= 1 && p.ar_out.tp <= 8), "gemv: bad tensor-parallel size");
     const bool quant_bias = (wtype == W_Q4_K || wtype == W_Q5_K);
     if (quant_bias) smem += (size_t)T * (K / 16) * 4;
     DLP_REQUIRE(smem <= 200 * 1024, "gemv: activations (%zu B) do not fit in shared memory", smem);

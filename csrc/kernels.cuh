@@ -4,7 +4,24 @@
 
 namespace dlp {
 
-enum GemvOut : int { GV_STORE_F16 = 0, GV_STORE_F32 = 1, GV_ADD_F32 = 2, GV_SWIGLU_F16 = 3 };
+enum GemvOut : int { GV_STORE_F16 = 0, GV_STORE_F32 = 1, GV_ADD_F32 = 2, GV_SWIGLU_F16 = 3, GV_PUSH_F32 = 4 };
+
+// Fused tensor-parallel all-reduce around the decode mat-vecs (see gemv.cu, comm.cu).
+struct ArIn {                 // consumer: h_out = h_in + sum over ranks of buf[r]
+    const float* buf;         // local reduce buffer [tp][T][K] fp32 (nullptr: no all-reduce to consume)
+    const uint32_t* flags;    // local [tp] epoch flags written by the peers
+    const int* epoch;         // device-resident step counter (same value on every rank)
+    float* h_out;             // where CTA 0 stores the updated residual stream
+    int* error;               // set to 1 on wait timeout
+    int tp;
+};
+struct ArOut {                // producer: push this rank's partial rows to every peer
+    float* peer_buf[8];       // peer_buf[p] = base of peer p's reduce buffer for this site
+    uint32_t* peer_flags[8];  // peer_flags[p] = base of peer p's flag array for this site
+    const int* epoch;
+    unsigned* done_counter;   // local, zero-initialised
+    int rank, tp;
+};
 
 struct GemvParams {
     QWeight w0, w1;       // w1 only for the SwiGLU (gate, up) pair
@@ -15,6 +32,8 @@ struct GemvParams {
     int ldy;
     int out_mode;
     int T;
+    ArIn ar_in;
+    ArOut ar_out;
 };
 
 struct AttnParams {
@@ -48,6 +67,8 @@ int sample(const float* logits, int R, int V, int ld, int top_k, float top_p, fl
 int f32_to_f16(const float* in, __half* out, size_t n, cudaStream_t s);
 int attn_paged(const AttnParams& p, int D, cudaStream_t s);
 int attn_paged_static(AttnParams p, int D, cudaStream_t s);
+int ar_consume(const float* h_in, float* h_out, const ArIn& a, int K, int T, cudaStream_t s);
+int bump(int* ctr, cudaStream_t s);
 int attn_prefill(const __half* q, const __half* kc, const __half* vc, const int* bt_row, __half* out, int T, int pos0,
                  int Hq, int Hkv, int D, int page_size, cudaStream_t s);
 

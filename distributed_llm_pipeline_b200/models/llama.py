@@ -110,6 +110,12 @@ class LlamaEngine:
         f16, f32, i32 = torch.float16, torch.float32, torch.int32
         qkv_dim = (self.Hq + 2 * self.Hkv) * self.D
         self.h = torch.zeros(M, self.E, dtype=f32, device=dev)
+        self.fused_tp = bool(getattr(self.comm, "fused", False)) and self.comm.tp_size > 1 and not cfg.is_moe
+        if self.fused_tp:
+            if not self.comm.ready:
+                self.comm.setup(self.E, 2 * len(weights.layer_range))
+            self.hb = [self.h, torch.zeros(4, self.E, dtype=f32, device=dev)]   # ping-pong residual (decode rows only)
+            self.cur, self.pending = 0, None
         self.delta = torch.zeros(M, self.E, dtype=f32, device=dev)
         self.xn = torch.zeros(M, self.E, dtype=f16, device=dev)
         self.qkv32 = torch.zeros(min(M, 4), qkv_dim, dtype=f32, device=dev)
@@ -202,6 +208,29 @@ class LlamaEngine:
         else:
             ops.linear(lw.w_down, act, "add", out=h, scratch=self._scratch_for(lw.w_down))
 
+    def _layer_fused(self, il: int, T: int, attn_fn):
+        """Decode layer with the tensor-parallel all-reduces fused into the mat-vecs (parallel/fused.py):
+        row-parallel GEMVs push partial rows into every peer's reduce buffer, the following GEMV's prologue
+        sums them into the residual stream while it computes RMSNorm.  No NCCL call, no extra launch."""
+        lw, cfg, c = self.w.layers[il], self.cfg, self.comm
+        li = il - self.w.layer_range.start
+        hin = self.hb[self.cur]
+        if self.pending is not None:
+            c.gemv(lw.wqkv, hin, ops.OUT_F32, T, out=self.qkv32[:T], norm_w=lw.attn_norm, eps=cfg.rms_eps,
+                   ar_in=c.ar_in(self.pending, self.hb[1 - self.cur]))
+            self.cur ^= 1
+        else:
+            c.gemv(lw.wqkv, hin, ops.OUT_F32, T, out=self.qkv32[:T], norm_w=lw.attn_norm, eps=cfg.rms_eps)
+        q = ops.rope_kv(self.qkv32[:T], self.pos[:T], self.slot[:T], self.inv_freq, self.kv.k[il], self.kv.v[il], self.Hq,
+                        self.Hkv, self.D, cfg.rope_neox, q_out=self.q[:T])
+        att = attn_fn(il, q, T)
+        c.gemv(lw.wo, att, 4, T, ar_out=c.ar_out(2 * li))
+        act = c.gemv(lw.w_gate, self.hb[self.cur], ops.OUT_SWIGLU_F16, T, out=self.act[:T], w_up=lw.w_up, norm_w=lw.ffn_norm,
+                     eps=cfg.rms_eps, ar_in=c.ar_in(2 * li, self.hb[1 - self.cur]))
+        self.cur ^= 1
+        c.gemv(lw.w_down, act, 4, T, ar_out=c.ar_out(2 * li + 1))
+        self.pending = 2 * li + 1
+
     def _moe(self, lw, T: int, xn):
         """Top-k routed experts (softmax over all experts, top-k, renormalise: llama-graph.cpp:1039-1139).
         Round-1 implementation: router + expert selection on the host side of the stream (not graph-capturable)."""
@@ -242,9 +271,28 @@ class LlamaEngine:
     def _embed(self, T: int, ids: torch.Tensor | None = None):
         ops.dequant_rows(self.w.tok_embd, self.tokens[:T] if ids is None else ids, out=self.h[:T])
 
-    def _run_layers(self, T: int, attn_fn):
+    def _run_layers(self, T: int, attn_fn, fused: bool = False):
+        if fused:
+            self.cur, self.pending = 0, None
+            self.comm.begin_step()
+            for il in self.w.layer_range:
+                self._layer_fused(il, T, attn_fn)
+            return
         for il in self.w.layer_range:
             self._layer(il, T, attn_fn)
+
+    def _finish_fused(self, T: int):
+        """Fold the last pending all-reduce: into the lm_head prologue (last stage) or a stand-alone consumer."""
+        c, cfg = self.comm, self.cfg
+        hin, hout = self.hb[self.cur], self.hb[1 - self.cur]
+        if self.last_stage:
+            c.gemv(self.w.lm_head, hin, ops.OUT_F32, T, out=self.logits[:T], norm_w=self.w.out_norm, eps=cfg.rms_eps,
+                   ar_in=c.ar_in(self.pending, hout))
+            return c.allgather_logits(self.logits[:T], self.w.vocab_range, cfg.vocab_size)
+        c.consume(hin, hout, self.pending, T)
+        if self.cur == 0:           # hand-off buffer for the next stage is always self.h
+            self.h[:T].copy_(hout[:T])
+        return None
 
     def _head(self, rows: torch.Tensor | slice, n: int) -> torch.Tensor:
         """logits for `n` rows of h (already gathered to the front of the xn buffer) -> self.logits[:n]."""
@@ -296,9 +344,14 @@ class LlamaEngine:
         ops.advance(self.seq_len_dev, self.active, self.pos, self.slot, self.kv_len, self.kv.block_table, self.page_size, B)
         if self.first_stage:
             self._embed(B, self.next_tok[:B])  # input ids = previously sampled (or host-provided) tokens
-        self._run_layers(B, self._attn_decode)
+        fused = self.fused_tp and B in (1, 2, 4)
+        self._run_layers(B, self._attn_decode, fused)
+        if fused:
+            lg = self._finish_fused(B)
         if self.last_stage:
-            lg = self._head(slice(0, B), B)
+            if not fused:
+                lg = self._head(slice(0, B), B)
+            self.logits_full = lg  # full-vocab logits (gathered across TP ranks); static across graph replays
             if sample:
                 s = self.sampling
                 ops.sample(lg, s["top_k"], s["top_p"], s["min_p"], s["temp"], s["seed"], self.step_ctr, out=self.next_tok[:B])
@@ -334,7 +387,7 @@ class LlamaEngine:
             self.seqs[sid].length += 1
         if not self.last_stage:
             return self.h[:B]
-        return self.next_tok[:B] if sample else self.logits[:B]
+        return self.next_tok[:B] if sample else self.logits_full[:B]
 
     def _capture(self, B: int, sample: bool):
         # warm-up (also lets every kernel set its attributes), then roll back the bookkeeping it advanced

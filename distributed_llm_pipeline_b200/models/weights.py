@@ -96,7 +96,18 @@ def load_weights(src: str | GGUFModelFiles, device, layer_range: range | None = 
         if sub is not None:  # one expert of a stacked [n_expert, N, K] tensor
             raw = raw[sub]
             shape = shape[1:]
-        raw2, shp = slice_raw(raw, t.ggml_type, shape, rows, cols)
+        try:
+            raw2, shp = slice_raw(raw, t.ggml_type, shape, rows, cols)
+        except ValueError:
+            # K range not aligned to the quant block (tiny models / odd TP sizes): decode once, slice densely, keep fp16
+            from ..gguf.quants import dequantize, quantize
+            dense = dequantize(raw, t.ggml_type, shape)
+            if rows is not None:
+                dense = dense[rows[0]:rows[1]]
+            if cols is not None:
+                dense = dense[:, cols[0]:cols[1]]
+            dense = np.ascontiguousarray(dense)
+            return DeviceWeight.from_raw(quantize(dense, GGMLType.F16), GGMLType.F16, dense.shape, dev)
         return DeviceWeight.from_raw(raw2, t.ggml_type, shp, dev)
 
     layers: dict[int, LayerWeights] = {}

@@ -1,0 +1,152 @@
+"""Tensor-parallel communicator whose all-reduce lives *inside* the decode mat-vec kernels.
+
+North-star item: "the column->row GEMM pair fuses the collective into the kernel: GEMM -> reduce/all-reduce issues
+NVSwitch P2P stores from inside the kernel".  Decode (T <= 4) path:
+
+    o_proj / down GEMV (row-parallel, K shard)  --epilogue-->  st.global of the partial rows into EVERY peer's
+                                                               reduce buffer + st.release.sys of an epoch flag
+    next GEMV (QKV / gate+up / lm_head)         <--prologue--  ld.acquire.sys on the tp flags, then
+                                                               h = h + sum_r partial[r] fused with RMSNorm
+
+so a layer needs no separate collective launch and no NCCL call.  Buffers are symmetric allocations mapped
+into every rank through CUDA IPC (`csrc/comm.cu`).  Larger token counts (prefill, big decode batches) use the
+NCCL path of :class:`NcclComm` - that path is also the A/B baseline the spec asks to keep.
+
+Reference counterpart: `ggml_cuda_op_mul_mat` broadcast + gather through a hub GPU (`ggml-cuda.cu:1451-1769`).
+"""
+from __future__ import annotations
+
+import ctypes as C
+
+import torch
+import torch.distributed as dist
+
+from ..ops import lib as _lib
+from .comm import NcclComm
+
+MAX_T = 4  # token rows per site in the fused path
+
+
+class dlp_ar_in(C.Structure):
+    _fields_ = [("buf", C.c_void_p), ("flags", C.c_void_p), ("epoch", C.c_void_p), ("h_out", C.c_void_p),
+                ("error", C.c_void_p), ("tp", C.c_int32), ("reserved", C.c_int32)]
+
+
+class dlp_ar_out(C.Structure):
+    _fields_ = [("peer_buf", C.c_void_p * 8), ("peer_flags", C.c_void_p * 8), ("epoch", C.c_void_p),
+                ("done_counter", C.c_void_p), ("rank", C.c_int32), ("tp", C.c_int32)]
+
+
+class FusedComm(NcclComm):
+    fused = True
+
+    def __init__(self, grid, n_embd: int | None = None, n_sites: int | None = None):
+        super().__init__(grid.tp_group, grid.tp, grid.tp_rank)
+        self.grid = grid
+        self.device = grid.device
+        self.lib = _lib.load()
+        self._declare()
+        self.ready = False
+        self.base = None
+        self.peers: list[int] = []
+        if n_embd is not None and n_sites is not None:
+            self.setup(n_embd, n_sites)
+
+    def _declare(self):
+        L, vp, i32 = self.lib, C.c_void_p, C.c_int
+        W = C.POINTER(_lib.dlp_weight)
+        L.dlp_gemv_tp.restype = i32
+        L.dlp_gemv_tp.argtypes = [W, W, vp, vp, C.c_float, vp, i32, i32, i32, C.POINTER(dlp_ar_in), C.POINTER(dlp_ar_out), vp]
+        L.dlp_ar_consume.restype = i32
+        L.dlp_ar_consume.argtypes = [vp, vp, C.POINTER(dlp_ar_in), i32, i32, vp]
+        L.dlp_bump.restype = i32
+        L.dlp_bump.argtypes = [vp, vp]
+        L.dlp_symm_alloc.restype = i32
+        L.dlp_symm_alloc.argtypes = [C.c_size_t, C.POINTER(vp)]
+        L.dlp_ipc_export.restype = i32
+        L.dlp_ipc_export.argtypes = [vp, vp]
+        L.dlp_ipc_import.restype = i32
+        L.dlp_ipc_import.argtypes = [vp, C.POINTER(vp)]
+
+    # ---- set-up: one symmetric allocation per rank, handles exchanged over the process group --------------
+    def setup(self, n_embd: int, n_sites: int):
+        tp = self.tp_size
+        self.E, self.n_sites = n_embd, n_sites
+        self.buf_bytes = tp * MAX_T * n_embd * 4
+        self.site_stride = self.buf_bytes + 256          # reduce buffer + flag line
+        total = n_sites * self.site_stride
+        p = C.c_void_p()
+        _lib.check(self.lib.dlp_symm_alloc(total, C.byref(p)), "symm_alloc")
+        self.base = p.value
+        handle = (C.c_char * 64)()
+        _lib.check(self.lib.dlp_ipc_export(self.base, handle), "ipc_export")
+        mine = bytes(handle)
+        gathered: list = [None] * tp
+        dist.all_gather_object(gathered, mine, group=self.group)
+        self.peers = []
+        for r, h in enumerate(gathered):
+            if r == self.tp_rank:
+                self.peers.append(self.base)
+                continue
+            q = C.c_void_p()
+            hb = (C.c_char * 64).from_buffer_copy(h)
+            _lib.check(self.lib.dlp_ipc_import(hb, C.byref(q)), "ipc_import")
+            self.peers.append(q.value)
+        self.epoch = torch.zeros(1, dtype=torch.int32, device=self.device)
+        self.done = torch.zeros(1, dtype=torch.int32, device=self.device)
+        self.error = torch.zeros(1, dtype=torch.int32, device=self.device)
+        self._in: dict[int, dlp_ar_in] = {}
+        self._out: dict[int, dlp_ar_out] = {}
+        dist.barrier(group=self.group)
+        self.ready = True
+
+    def ar_in(self, site: int, h_out: torch.Tensor) -> dlp_ar_in:
+        key = (site, h_out.data_ptr())
+        d = self._in.get(key)
+        if d is None:
+            b = self.base + site * self.site_stride
+            d = dlp_ar_in(b, b + self.buf_bytes, self.epoch.data_ptr(), h_out.data_ptr(), self.error.data_ptr(), self.tp_size, 0)
+            self._in[key] = d
+        return d
+
+    def ar_out(self, site: int) -> dlp_ar_out:
+        d = self._out.get(site)
+        if d is None:
+            d = dlp_ar_out()
+            for r in range(self.tp_size):
+                b = self.peers[r] + site * self.site_stride
+                d.peer_buf[r] = b
+                d.peer_flags[r] = b + self.buf_bytes
+            d.epoch = self.epoch.data_ptr()
+            d.done_counter = self.done.data_ptr()
+            d.rank, d.tp = self.tp_rank, self.tp_size
+            self._out[site] = d
+        return d
+
+    # ---- per-step -----------------------------------------------------------------------------------
+    def begin_step(self):
+        """Advance the epoch (device-side, graph-capturable); every rank calls it once per forward pass."""
+        from ..ops import api as ops
+        _lib.check(self.lib.dlp_bump(self.epoch.data_ptr(), torch.cuda.current_stream().cuda_stream), "bump")
+        ops._count()
+
+    def gemv(self, w, x, out_mode: int, T: int, out=None, w_up=None, norm_w=None, eps: float = 0.0, ar_in=None, ar_out=None):
+        from ..ops import api as ops
+        _lib.check(self.lib.dlp_gemv_tp(w.ref(), w_up.ref() if w_up is not None else None, x.data_ptr(),
+                                        None if norm_w is None else norm_w.data_ptr(), eps,
+                                        None if out is None else out.data_ptr(), 0 if out is None else out.stride(0), out_mode, T,
+                                        None if ar_in is None else C.byref(ar_in), None if ar_out is None else C.byref(ar_out),
+                                        torch.cuda.current_stream().cuda_stream), "gemv_tp")
+        ops._count()
+        return out
+
+    def consume(self, h_in: torch.Tensor, h_out: torch.Tensor, site: int, T: int):
+        from ..ops import api as ops
+        d = self.ar_in(site, h_out)
+        _lib.check(self.lib.dlp_ar_consume(h_in.data_ptr(), h_out.data_ptr(), C.byref(d), self.E, T,
+                                           torch.cuda.current_stream().cuda_stream), "ar_consume")
+        ops._count()
+
+    def check_error(self):
+        if int(self.error.item()):
+            raise RuntimeError("fused all-reduce: a peer did not signal within the timeout (ranks diverged or died)")

@@ -124,6 +124,44 @@ int dlp_sample(const float* logits, int R, int V, int ld, int top_k, float top_p
 
 int dlp_f32_to_f16(const float* in, void* out, size_t n, void* stream);
 
+/* ---- tensor-parallel decode with the all-reduce fused into the mat-vecs (NVLink peer stores, no NCCL) ----
+ * Each rank owns a reduce buffer [tp][T][E] fp32 and a flag array [tp] per all-reduce site, mapped by all peers
+ * (dlp_symm_alloc + dlp_ipc_export / dlp_ipc_import).  A row-parallel mat-vec launched with out_mode
+ * DLP_OUT_PUSH_F32 stores its partial rows into every peer's buffer and then publishes the epoch flag; the next
+ * mat-vec (or dlp_ar_consume) launched with a dlp_ar_in waits for the tp flags and folds
+ *   h_out = h_in + sum_r buf[r]     into its RMSNorm prologue.
+ * `epoch` is a device-resident counter with the same value on every rank (dlp_bump once per forward pass).
+ * ref: the hub-and-spoke broadcast/gather around split matmuls (ggml-cuda/ggml-cuda.cu:1680-1744) - no reduce exists there. */
+enum { DLP_OUT_PUSH_F32 = 4 };
+typedef struct dlp_ar_in {
+    const float* buf;        /* local reduce buffer of this site (NULL: nothing to consume) */
+    const uint32_t* flags;   /* local flags [tp] */
+    const int32_t* epoch;
+    float* h_out;            /* updated residual stream (written by CTA 0) */
+    int32_t* error;          /* optional: set to 1 if a peer never signalled */
+    int32_t tp;
+    int32_t reserved;
+} dlp_ar_in;
+typedef struct dlp_ar_out {
+    float* peer_buf[8];      /* this site's reduce buffer on every rank (own rank included) */
+    uint32_t* peer_flags[8];
+    const int32_t* epoch;
+    uint32_t* done_counter;  /* local scratch counter, zero-initialised, shared by all sites */
+    int32_t rank;
+    int32_t tp;
+} dlp_ar_out;
+int dlp_gemv_tp(const dlp_weight* w0, const dlp_weight* w1, const void* x, const float* norm_w, float eps, void* y,
+                int ldy, int out_mode, int T, const dlp_ar_in* ar_in, const dlp_ar_out* ar_out, void* stream);
+int dlp_ar_consume(const float* h_in, float* h_out, const dlp_ar_in* ar_in, int E, int T, void* stream);
+int dlp_bump(int32_t* counter, void* stream);
+/* symmetric memory plumbing (set-up time only; these do allocate / synchronise) */
+int dlp_symm_alloc(size_t bytes, void** ptr);
+int dlp_symm_free(void* ptr);
+int dlp_ipc_export(void* ptr, void* handle64);
+int dlp_ipc_import(const void* handle64, void** ptr);
+int dlp_ipc_close(void* ptr);
+int dlp_memcpy_d2h(void* dst, const void* src, size_t bytes);
+
 #ifdef __cplusplus
 }
 #endif

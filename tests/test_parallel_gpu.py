@@ -1,0 +1,49 @@
+"""Multi-GPU paths on real devices (skipped below 2 GPUs): TP over NCCL, TP with the all-reduce fused into the
+mat-vec kernels (NVLink peer stores), and a 2-stage pipeline - each against the fp32 oracle."""
+import os
+import subprocess
+import sys
+
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+HERE = os.path.dirname(os.path.abspath(__file__))
+
+
+def _torchrun(n, args, port):
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={n}", "--master-addr", "127.0.0.1",
+           "--master-port", str(port), os.path.join(HERE, "mp_worker.py")] + args
+    return subprocess.run(cmd, capture_output=True, text=True, timeout=600)
+
+
+def _need(n):
+    if torch.cuda.device_count() < n:
+        pytest.skip(f"needs {n} GPUs")
+
+
+@pytest.mark.parametrize("impl", ["nccl", "fused"])
+@pytest.mark.parametrize("batch", [1, 2, 3])
+def test_tp2_gpu(tmp_models, impl, batch):
+    _need(2)
+    r = _torchrun(2, ["--model", tmp_models[("tiny128", "F16")], "--device", "cuda", "--impl", impl, "--batch", str(batch)], 29711 + batch)
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
+    assert "MP_RESULT" in r.stdout
+
+
+def test_tp2_fused_quantised(tmp_models):
+    _need(2)
+    r = _torchrun(2, ["--model", tmp_models[("tiny128", "Q4_K_M")], "--device", "cuda", "--impl", "fused"], 29721)
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
+
+
+def test_pp2_gpu(tmp_models):
+    _need(2)
+    r = _torchrun(2, ["--model", tmp_models[("tiny128", "F16")], "--device", "cuda", "--pp", "2", "--batch", "2"], 29731)
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
+
+
+def test_pp2_tp2_fused_gpu(tmp_models):
+    _need(4)
+    r = _torchrun(4, ["--model", tmp_models[("tiny128", "F16")], "--device", "cuda", "--pp", "2", "--impl", "fused"], 29741)
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
