@@ -157,6 +157,18 @@ class LlamaEngine:
     def seq_len(self, sid: int) -> int:
         return self.seqs[sid].length
 
+    def truncate_seq(self, sid: int, new_len: int):
+        """Keep only the first `new_len` cached tokens of a sequence (prompt-prefix reuse, rollback after errors).
+        Parity: `llama_memory_seq_rm(seq, p0=new_len, p1=-1)` (`llama-kv-cache.cpp:224-320`); pages past the cut
+        return to the free list."""
+        seq = self.seqs[sid]
+        new_len = max(0, min(new_len, seq.length))
+        keep_pages = (new_len + self.page_size - 1) // self.page_size
+        while len(seq.pages) > keep_pages:
+            self.kv.free.append(seq.pages.pop())
+        seq.length = new_len
+        self.seq_len_dev[sid] = new_len
+
     def _scratch_for(self, *ws):
         need = 0
         for w in ws:
@@ -377,9 +389,10 @@ class LlamaEngine:
         graphable = (use_graph and self.device.type == "cuda" and not self.cfg.is_moe
                      and not getattr(self.comm, "no_graph", False))
         if graphable:
-            g = self._graphs.get((B, sample))
+            key = (B, sample) + (tuple(self.sampling.values()) if sample else ())  # sampler scalars are baked into the graph
+            g = self._graphs.get(key)
             if g is None:
-                g = self._capture(B, sample)
+                g = self._capture(B, sample, key)
             g.replay()
         else:
             self._decode_body(B, sample)
@@ -389,7 +402,7 @@ class LlamaEngine:
             return self.h[:B]
         return self.next_tok[:B] if sample else self.logits_full[:B]
 
-    def _capture(self, B: int, sample: bool):
+    def _capture(self, B: int, sample: bool, key=None):
         # warm-up (also lets every kernel set its attributes), then roll back the bookkeeping it advanced
         saved = self.seq_len_dev.clone()
         saved_ctr = self.step_ctr.clone()
@@ -408,7 +421,7 @@ class LlamaEngine:
         self.launches_per_graph[(B, sample)] = ops.launch_count - n0
         self.seq_len_dev.copy_(saved)
         self.step_ctr.copy_(saved_ctr)
-        self._graphs[(B, sample)] = g
+        self._graphs[key or (B, sample)] = g
         return g
 
     # ---- convenience ------------------------------------------------------------------------------

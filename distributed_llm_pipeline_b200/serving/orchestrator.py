@@ -1,0 +1,372 @@
+"""HTTP / SSE orchestrator, wire-compatible with the reference's Rust front-end.
+
+Parity (`orchestrator/src/main.rs`): `POST /chat` with `{"prompt": string}` answers `text/event-stream`; every event is
+`data: {"msg_type":"log"|"token","content":string}\\n\\n` (`:18-27,63-95`), a keep-alive comment is sent every second
+(`:97`), CORS is permissive and everything else falls back to static files (`:100-111`); default port 3005.  What differs on
+purpose: the engine is persistent (the reference spawns `llama-cli` and reloads the model for every request), requests
+queue for slots instead of racing, `token` events carry only generated text (the reference forwards raw stdout incl. banners),
+multi-byte UTF-8 is never split across events, a disconnecting client cancels its request, and failures arrive as a `log`
+event instead of a panicked handler.  Extra routes mirror `llama-server` (`tools/server/server.cpp:164-197`): `/health`,
+`/metrics`, `/slots`, `/props`, `/completion`, `/tokenize`, `/detokenize`, `/v1/models`, `/v1/completions`,
+`/v1/chat/completions`.
+"""
+from __future__ import annotations
+
+import argparse
+import asyncio
+import json
+import mimetypes
+import os
+import time
+import uuid
+
+from .sampler import SamplingParams
+from .scheduler import Request, Scheduler
+
+STATIC_DIR = os.path.join(os.path.dirname(os.path.abspath(__file__)), "static")
+CORS = [("access-control-allow-origin", "*"), ("vary", "origin, access-control-request-method, access-control-request-headers")]
+
+
+def sse_event(msg_type: str, content: str) -> bytes:
+    """One server-sent event in the reference's wire format (serde field order: msg_type, content)."""
+    return b"data: " + json.dumps({"msg_type": msg_type, "content": content}, ensure_ascii=False, separators=(",", ":")).encode() + b"\n\n"
+
+
+KEEPALIVE = b":\n\n"
+
+
+def apply_chat_template(meta: dict, messages: list[dict]) -> str:
+    """Minimal chat formatting: Llama-3 and ChatML families are recognised from the GGUF template string; models without a
+    template (random-init checkpoints) get the plain concatenation.  (ref: built-in templates, `llama.cpp/src/llama-chat.cpp`)"""
+    tmpl = str(meta.get("tokenizer.chat_template", ""))
+    if "<|start_header_id|>" in tmpl:
+        out = "".join(f"<|start_header_id|>{m['role']}<|end_header_id|>\n\n{m['content']}<|eot_id|>" for m in messages)
+        return out + "<|start_header_id|>assistant<|end_header_id|>\n\n"
+    if "<|im_start|>" in tmpl:
+        out = "".join(f"<|im_start|>{m['role']}\n{m['content']}<|im_end|>\n" for m in messages)
+        return out + "<|im_start|>assistant\n"
+    if "[INST]" in tmpl:
+        out = ""
+        for m in messages:
+            out += f"[INST] {m['content']} [/INST]" if m["role"] == "user" else f" {m['content']}</s>"
+        return out
+    return "\n".join(m["content"] for m in messages)
+
+
+class Orchestrator:
+    def __init__(self, scheduler: Scheduler, model_info: dict | None = None, static_dir: str = STATIC_DIR, n_predict: int = 200,
+                 startup_logs: list[str] | None = None):
+        self.sched = scheduler
+        self.info = model_info or {}
+        self.static_dir = static_dir
+        self.n_predict = n_predict
+        self.startup_logs = startup_logs or []
+        self.t_start = time.time()
+        self._server: asyncio.AbstractServer | None = None
+
+    # ---- tiny HTTP/1.1 layer ------------------------------------------------------------------------
+    async def _read_request(self, reader: asyncio.StreamReader):
+        line = await reader.readline()
+        if not line:
+            return None
+        try:
+            method, target, _ = line.decode("latin1").split(" ", 2)
+        except ValueError:
+            return None
+        headers = {}
+        while True:
+            h = await reader.readline()
+            if h in (b"\r\n", b"\n", b""):
+                break
+            k, _, v = h.decode("latin1").partition(":")
+            headers[k.strip().lower()] = v.strip()
+        body = b""
+        n = int(headers.get("content-length", "0") or 0)
+        if n > 64 << 20:
+            raise ValueError("body too large")
+        if n:
+            body = await reader.readexactly(n)
+        return method.upper(), target, headers, body
+
+    @staticmethod
+    def _head(status: str, headers: list[tuple[str, str]]) -> bytes:
+        return (f"HTTP/1.1 {status}\r\n" + "".join(f"{k}: {v}\r\n" for k, v in headers) + "\r\n").encode("latin1")
+
+    async def _send(self, writer, status: str, body: bytes, ctype: str = "application/json", extra=()):
+        writer.write(self._head(status, [("content-type", ctype), ("content-length", str(len(body)))] + CORS + list(extra)) + body)
+        await writer.drain()
+
+    async def _json(self, writer, obj, status="200 OK"):
+        await self._send(writer, status, json.dumps(obj).encode())
+
+    async def handle(self, reader: asyncio.StreamReader, writer: asyncio.StreamWriter):
+        try:
+            while True:
+                req = await self._read_request(reader)
+                if req is None:
+                    break
+                method, target, headers, body = req
+                path = target.split("?", 1)[0]
+                keep = await self.route(method, path, headers, body, reader, writer)
+                if not keep or headers.get("connection", "").lower() == "close":
+                    break
+        except (ConnectionError, asyncio.IncompleteReadError, ValueError):
+            pass
+        finally:
+            try:
+                writer.close()
+            except Exception:
+                pass
+
+    async def route(self, method, path, headers, body, reader, writer) -> bool:
+        if method == "OPTIONS":  # permissive CORS pre-flight (tower-http CorsLayer::permissive)
+            writer.write(self._head("200 OK", CORS + [("access-control-allow-methods", "*"), ("access-control-allow-headers", "*"),
+                                                       ("content-length", "0")]))
+            await writer.drain()
+            return True
+        try:
+            if method == "POST" and path == "/chat":
+                await self.chat(body, writer)
+                return False
+            if method == "POST" and path in ("/completion", "/completions", "/v1/completions"):
+                return await self.completion(json.loads(body or b"{}"), writer, openai=path.startswith("/v1"))
+            if method == "POST" and path == "/v1/chat/completions":
+                return await self.chat_completions(json.loads(body or b"{}"), writer)
+            if method == "POST" and path == "/tokenize":
+                d = json.loads(body or b"{}")
+                await self._json(writer, {"tokens": self.sched.tok.encode(d.get("content", ""), add_bos=bool(d.get("add_special", False)))})
+                return True
+            if method == "POST" and path == "/detokenize":
+                await self._json(writer, {"content": self.sched.tok.decode(json.loads(body or b"{}").get("tokens", []), False)})
+                return True
+            if method == "GET" and path == "/health":
+                await self._json(writer, {"status": "ok"})
+                return True
+            if method == "GET" and path == "/metrics":
+                await self._send(writer, "200 OK", self.sched.metrics.prometheus().encode(), "text/plain; version=0.0.4")
+                return True
+            if method == "GET" and path == "/slots":
+                await self._json(writer, self.sched.slots_info())
+                return True
+            if method == "GET" and path == "/props":
+                await self._json(writer, {"model": self.info, "total_slots": self.sched.n_slots, "n_ctx": self.sched.eng.n_ctx,
+                                          "uptime_s": round(time.time() - self.t_start, 1)})
+                return True
+            if method == "GET" and path == "/v1/models":
+                await self._json(writer, {"object": "list", "data": [{"id": self.info.get("name", "model"), "object": "model",
+                                                                        "created": int(self.t_start), "owned_by": "dlp_b200"}]})
+                return True
+            if method in ("GET", "HEAD"):
+                return await self.static(path, writer, head=(method == "HEAD"))
+            await self._json(writer, {"error": "not found"}, "404 Not Found")
+            return True
+        except json.JSONDecodeError as e:
+            await self._json(writer, {"error": f"invalid JSON: {e}"}, "400 Bad Request")
+            return True
+
+    # ---- static files (ServeDir fallback) -----------------------------------------------------------------
+    async def static(self, path: str, writer, head=False) -> bool:
+        rel = path.lstrip("/") or "index.html"
+        full = os.path.realpath(os.path.join(self.static_dir, rel))
+        root = os.path.realpath(self.static_dir)
+        if os.path.isdir(full):
+            full = os.path.join(full, "index.html")
+        if not (full == root or full.startswith(root + os.sep)) or not os.path.isfile(full):
+            await self._send(writer, "404 Not Found", b"", "text/plain")
+            return True
+        data = open(full, "rb").read()
+        ctype = mimetypes.guess_type(full)[0] or "application/octet-stream"
+        if ctype.startswith("text/") or ctype in ("application/javascript", "application/json"):
+            ctype += "; charset=utf-8" if "charset" not in ctype else ""
+        await self._send(writer, "200 OK", b"" if head else data, ctype)
+        return True
+
+    # ---- the reference route ----------------------------------------------------------------------------------
+    async def _stream_request(self, req: Request, writer, fmt):
+        """Submit `req`, forward its events formatted by `fmt(kind, content) -> bytes | None`, 1 s keep-alives in between."""
+        loop = asyncio.get_running_loop()
+        q: asyncio.Queue = asyncio.Queue()
+        req.on_event = lambda kind, content: loop.call_soon_threadsafe(q.put_nowait, (kind, content))
+        self.sched.submit(req)
+        try:
+            while True:
+                try:
+                    kind, content = await asyncio.wait_for(q.get(), timeout=1.0)
+                except asyncio.TimeoutError:
+                    writer.write(KEEPALIVE)
+                    await writer.drain()
+                    continue
+                data = fmt(kind, content)
+                if data:
+                    writer.write(data)
+                    await writer.drain()
+                if kind == "done":
+                    break
+        except (ConnectionError, asyncio.CancelledError):
+            self.sched.cancel(req)  # client went away: free the slot (the reference leaves the child running)
+            raise
+
+    async def chat(self, body: bytes, writer):
+        try:
+            payload = json.loads(body or b"{}")
+            prompt = payload["prompt"]
+            if not isinstance(prompt, str):
+                raise KeyError
+        except (json.JSONDecodeError, KeyError, TypeError):
+            # axum's Json extractor rejects malformed bodies with 422 / 400
+            await self._send(writer, "422 Unprocessable Entity", b"Failed to deserialize the JSON body into the target type", "text/plain; charset=utf-8")
+            return
+        writer.write(self._head("200 OK", [("content-type", "text/event-stream"), ("cache-control", "no-cache")] + CORS +
+                                [("connection", "close")]))
+        for line in self.startup_logs:  # the distributed-placement "proof" lines the UI highlights (RPC / offloaded)
+            writer.write(sse_event("log", line))
+        await writer.drain()
+        req = Request(prompt=prompt, n_predict=self.n_predict, sampling=SamplingParams())
+
+        def fmt(kind, content):
+            if kind == "token":
+                return sse_event("token", content)
+            if kind == "log":
+                return sse_event("log", content)
+            if kind == "error":
+                return sse_event("log", f"error: {content}\n")
+            return None
+
+        await self._stream_request(req, writer, fmt)
+
+    # ---- llama-server style / OpenAI style completions -----------------------------------------------------------
+    def _sampling_from(self, d: dict) -> SamplingParams:
+        return SamplingParams(temperature=float(d.get("temperature", 0.8)), top_k=int(d.get("top_k", 40)), top_p=float(d.get("top_p", 0.95)),
+                              min_p=float(d.get("min_p", 0.05)), typical_p=float(d.get("typical_p", 1.0)),
+                              repeat_penalty=float(d.get("repeat_penalty", 1.0)), frequency_penalty=float(d.get("frequency_penalty", 0.0)),
+                              presence_penalty=float(d.get("presence_penalty", 0.0)), seed=int(d.get("seed", 0) if d.get("seed", 0) >= 0 else 0))
+
+    async def completion(self, d: dict, writer, openai=False) -> bool:
+        stop = d.get("stop") or []
+        stop = [stop] if isinstance(stop, str) else list(stop)
+        n_predict = int(d.get("n_predict", d.get("max_tokens", self.n_predict)))
+        req = Request(prompt=d.get("prompt", ""), n_predict=n_predict if n_predict > 0 else self.sched.eng.n_ctx,
+                      sampling=self._sampling_from(d), stop=stop, cache_prompt=bool(d.get("cache_prompt", True)),
+                      ignore_eos=bool(d.get("ignore_eos", False)))
+        rid = "cmpl-" + uuid.uuid4().hex[:24]
+        if d.get("stream"):
+            writer.write(self._head("200 OK", [("content-type", "text/event-stream"), ("cache-control", "no-cache")] + CORS + [("connection", "close")]))
+
+            def fmt(kind, content):
+                if kind == "token":
+                    obj = ({"id": rid, "object": "text_completion", "choices": [{"index": 0, "text": content, "finish_reason": None}]}
+                           if openai else {"content": content, "stop": False})
+                    return b"data: " + json.dumps(obj).encode() + b"\n\n"
+                if kind == "done":
+                    obj = ({"id": rid, "object": "text_completion", "choices": [{"index": 0, "text": "", "finish_reason": content}]}
+                           if openai else {"content": "", "stop": True, "stop_type": content, "timings": req.timings()})
+                    return b"data: " + json.dumps(obj).encode() + b"\n\n" + (b"data: [DONE]\n\n" if openai else b"")
+                return None
+
+            await self._stream_request(req, writer, fmt)
+            return False
+        await self._run_blocking(req)
+        if openai:
+            await self._json(writer, {"id": rid, "object": "text_completion", "created": int(time.time()), "model": self.info.get("name", "model"),
+                                      "choices": [{"index": 0, "text": req.text, "finish_reason": req.finish_reason}],
+                                      "usage": {"prompt_tokens": len(req.prompt_ids), "completion_tokens": len(req.output_ids),
+                                                "total_tokens": len(req.prompt_ids) + len(req.output_ids)}})
+        else:
+            await self._json(writer, {"content": req.text, "stop": True, "stop_type": req.finish_reason, "tokens_predicted": len(req.output_ids),
+                                      "tokens_evaluated": len(req.prompt_ids), "timings": req.timings()})
+        return True
+
+    async def chat_completions(self, d: dict, writer) -> bool:
+        prompt = apply_chat_template(self.info.get("metadata", {}), d.get("messages", []))
+        n_predict = int(d.get("max_tokens", d.get("max_completion_tokens", self.n_predict)))
+        stop = d.get("stop") or []
+        req = Request(prompt=prompt, n_predict=n_predict, sampling=self._sampling_from(d), stop=[stop] if isinstance(stop, str) else list(stop))
+        rid = "chatcmpl-" + uuid.uuid4().hex[:24]
+        if d.get("stream"):
+            writer.write(self._head("200 OK", [("content-type", "text/event-stream"), ("cache-control", "no-cache")] + CORS + [("connection", "close")]))
+
+            def fmt(kind, content):
+                base = {"id": rid, "object": "chat.completion.chunk", "created": int(time.time()), "model": self.info.get("name", "model")}
+                if kind == "token":
+                    base["choices"] = [{"index": 0, "delta": {"content": content}, "finish_reason": None}]
+                    return b"data: " + json.dumps(base).encode() + b"\n\n"
+                if kind == "done":
+                    base["choices"] = [{"index": 0, "delta": {}, "finish_reason": content}]
+                    return b"data: " + json.dumps(base).encode() + b"\n\ndata: [DONE]\n\n"
+                return None
+
+            await self._stream_request(req, writer, fmt)
+            return False
+        await self._run_blocking(req)
+        await self._json(writer, {"id": rid, "object": "chat.completion", "created": int(time.time()), "model": self.info.get("name", "model"),
+                                  "choices": [{"index": 0, "message": {"role": "assistant", "content": req.text}, "finish_reason": req.finish_reason}],
+                                  "usage": {"prompt_tokens": len(req.prompt_ids), "completion_tokens": len(req.output_ids),
+                                            "total_tokens": len(req.prompt_ids) + len(req.output_ids)}, "timings": req.timings()})
+        return True
+
+    async def _run_blocking(self, req: Request):
+        loop = asyncio.get_running_loop()
+        fut = loop.create_future()
+        req.on_event = lambda kind, content: (kind == "done") and loop.call_soon_threadsafe(lambda: fut.done() or fut.set_result(True))
+        self.sched.submit(req)
+        await fut
+
+    # ---- lifecycle ----------------------------------------------------------------------------------------
+    async def serve(self, host: str = "0.0.0.0", port: int = 3005):
+        self._server = await asyncio.start_server(self.handle, host, port, reuse_address=True)
+        async with self._server:
+            await self._server.serve_forever()
+
+
+def build_service(model: str, device: str = "cuda", n_ctx: int = 2048, n_slots: int = 4, n_batch: int = 2048, page_size: int = 64):
+    """Load a GGUF checkpoint and return (scheduler, model_info, startup_logs)."""
+    import torch
+
+    from ..gguf import open_gguf
+    from ..models.llama import LlamaEngine
+    from ..models.weights import load_weights
+    from ..utils.tokenizer import Tokenizer
+    dev = device if (device != "cuda" or torch.cuda.is_available()) else "cpu"
+    f = open_gguf(model)
+    t0 = time.time()
+    w = load_weights(f, dev)
+    eng = LlamaEngine(w, n_ctx=n_ctx, max_seqs=n_slots, page_size=page_size if dev != "cpu" else 16, max_batch_tokens=n_batch)
+    tok = Tokenizer(f.metadata)
+    cfg = w.cfg
+    logs = [
+        f"load: {os.path.basename(model)} | arch {cfg.arch} | {cfg.n_layer} layers | n_embd {cfg.n_embd} | vocab {cfg.vocab_size}\n",
+        f"load_tensors: offloaded {cfg.n_layer + 1}/{cfg.n_layer + 1} layers to GPU ({dev}), {w.nbytes() / 2**20:.1f} MiB in {time.time() - t0:.2f} s\n",
+        f"kv cache: {eng.kv.n_pages} pages x {eng.page_size} tokens ({eng.kv.bytes() / 2**20:.1f} MiB), {n_slots} slots, n_ctx {n_ctx}\n",
+    ]
+    info = {"name": str(f.metadata.get("general.name", os.path.basename(model))), "n_params": cfg.n_params(), "n_ctx_train": cfg.n_ctx_train,
+            "metadata": {"tokenizer.chat_template": f.metadata.get("tokenizer.chat_template", "")}}
+    sched = Scheduler(eng, tok, n_batch=n_batch)
+    return sched, info, logs
+
+
+def main(argv=None):
+    ap = argparse.ArgumentParser(description="dlp_b200 orchestrator (wire-compatible with the reference's /chat SSE API)")
+    ap.add_argument("-m", "--model", required=True)
+    ap.add_argument("--host", default=os.environ.get("DLP_HOST", "0.0.0.0"))
+    ap.add_argument("--port", type=int, default=int(os.environ.get("DLP_PORT", "3005")))
+    ap.add_argument("-c", "--ctx-size", type=int, default=2048)
+    ap.add_argument("-n", "--predict", type=int, default=200)
+    ap.add_argument("-np", "--parallel", type=int, default=4)
+    ap.add_argument("-b", "--batch-size", type=int, default=2048)
+    ap.add_argument("--device", default="cuda")
+    ap.add_argument("--static", default=STATIC_DIR)
+    a = ap.parse_args(argv)
+    sched, info, logs = build_service(a.model, a.device, a.ctx_size, a.parallel, a.batch_size)
+    sched.start()
+    orch = Orchestrator(sched, info, a.static, a.predict, logs)
+    print(f"dlp_b200 orchestrator ready: http://localhost:{a.port}", flush=True)
+    try:
+        asyncio.run(orch.serve(a.host, a.port))
+    except KeyboardInterrupt:
+        pass
+    finally:
+        sched.stop()
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,406 @@
+"""Serving core: request queue, slots, continuous batching with chunked prefill, stop conditions, timings, metrics.
+
+Parity: the slot engine of `llama-server` / `llama-cli` (`llama.cpp/tools/server/server-context.cpp`): slot state
+machine (`:34-41`), `update_slots` (`:1917-2860`) = add one token per generating slot, then prompt chunks up to
+`n_batch`, then decode and sample per slot; prompt-prefix reuse by longest common prefix (`:960-1060`); deferred
+requests when all slots are busy; per-request timings (`timings.prompt_per_second`, `predicted_per_second`) and the
+Prometheus counters of `/metrics` (`:3225-3300`).  Differences by design: the KV cache is paged so prefix reuse is a
+length truncation (no cell bookkeeping), decode runs as one CUDA-graph replay per step for whatever subset of slots is
+generating, and the default sampler chain runs on the device.
+"""
+from __future__ import annotations
+
+import itertools
+import threading
+import time
+from collections import deque
+from dataclasses import dataclass, field
+from enum import Enum
+from typing import Callable
+
+import torch
+
+from ..utils.tokenizer import StreamDecoder, Tokenizer
+from .sampler import Sampler, SamplingParams
+
+
+class SlotState(Enum):
+    IDLE = 0
+    PROMPT = 1
+    GENERATING = 2
+
+
+@dataclass
+class Request:
+    prompt: str | list[int]
+    n_predict: int = 200
+    sampling: SamplingParams = field(default_factory=SamplingParams)
+    stop: list[str] = field(default_factory=list)
+    on_event: Callable[[str, str], None] | None = None  # ("token" | "log" | "done" | "error", content)
+    ignore_eos: bool = False
+    cache_prompt: bool = True
+    id: int = 0
+    # filled in by the scheduler
+    prompt_ids: list[int] = field(default_factory=list)
+    output_ids: list[int] = field(default_factory=list)
+    text: str = ""
+    finish_reason: str | None = None
+    t_submit: float = 0.0
+    t_start: float = 0.0
+    t_first_token: float = 0.0
+    t_done: float = 0.0
+    n_prompt_processed: int = 0
+    n_prompt_cached: int = 0
+    done: threading.Event = field(default_factory=threading.Event)
+    cancelled: bool = False
+
+    def timings(self) -> dict:
+        p_ms = max(1e-6, (self.t_first_token - self.t_start) * 1e3) if self.t_first_token else 0.0
+        g_ms = max(1e-6, (self.t_done - self.t_first_token) * 1e3) if self.t_done and self.t_first_token else 0.0
+        n_gen = max(0, len(self.output_ids) - 1)
+        return {
+            "prompt_n": self.n_prompt_processed, "cache_n": self.n_prompt_cached, "prompt_ms": round(p_ms, 3),
+            "prompt_per_second": round(self.n_prompt_processed / p_ms * 1e3, 2) if p_ms else 0.0,
+            "predicted_n": len(self.output_ids), "predicted_ms": round(g_ms, 3),
+            "predicted_per_second": round(n_gen / g_ms * 1e3, 2) if g_ms and n_gen else 0.0,
+            "ttft_ms": round((self.t_first_token - self.t_submit) * 1e3, 3) if self.t_first_token else None,
+        }
+
+
+@dataclass
+class Slot:
+    idx: int
+    sid: int | None = None
+    state: SlotState = SlotState.IDLE
+    req: Request | None = None
+    cache_tokens: list[int] = field(default_factory=list)  # tokens whose KV is resident (prompt cache)
+    n_past: int = 0
+    sampler: Sampler | None = None
+    decoder: StreamDecoder | None = None
+    next_token: int = 0
+    t_last_used: float = 0.0
+
+
+class Metrics:
+    """Counters exported at /metrics (names follow the reference's Prometheus endpoint)."""
+
+    def __init__(self):
+        self.lock = threading.Lock()
+        self.c = dict(prompt_tokens_total=0, prompt_seconds_total=0.0, tokens_predicted_total=0,
+                      tokens_predicted_seconds_total=0.0, n_decode_total=0, n_busy_slots_total=0, n_tokens_max=0,
+                      requests_total=0, requests_failed_total=0)
+        self.g = dict(requests_processing=0, requests_deferred=0, kv_pages_free=0, kv_pages_total=0)
+
+    def add(self, **kw):
+        with self.lock:
+            for k, v in kw.items():
+                self.c[k] = self.c.get(k, 0) + v
+
+    def prometheus(self) -> str:
+        with self.lock:
+            c, g = dict(self.c), dict(self.g)
+        lines = []
+
+        def emit(name, kind, helptext, value):
+            lines.append(f"# HELP llamacpp:{name} {helptext}")
+            lines.append(f"# TYPE llamacpp:{name} {kind}")
+            lines.append(f"llamacpp:{name} {value}")
+
+        emit("prompt_tokens_total", "counter", "Number of prompt tokens processed.", c["prompt_tokens_total"])
+        emit("prompt_seconds_total", "counter", "Prompt process time", round(c["prompt_seconds_total"], 6))
+        emit("tokens_predicted_total", "counter", "Number of generation tokens processed.", c["tokens_predicted_total"])
+        emit("tokens_predicted_seconds_total", "counter", "Predict process time", round(c["tokens_predicted_seconds_total"], 6))
+        emit("n_decode_total", "counter", "Total number of decode steps", c["n_decode_total"])
+        emit("n_tokens_max", "counter", "Largest observed n_tokens.", c["n_tokens_max"])
+        emit("n_busy_slots_per_decode", "counter", "Average number of busy slots per decode step",
+             round(c["n_busy_slots_total"] / max(1, c["n_decode_total"]), 4))
+        emit("prompt_tokens_seconds", "gauge", "Average prompt throughput in tokens/s.",
+             round(c["prompt_tokens_total"] / c["prompt_seconds_total"], 3) if c["prompt_seconds_total"] else 0)
+        emit("predicted_tokens_seconds", "gauge", "Average generation throughput in tokens/s.",
+             round(c["tokens_predicted_total"] / c["tokens_predicted_seconds_total"], 3) if c["tokens_predicted_seconds_total"] else 0)
+        emit("requests_processing", "gauge", "Number of requests processing.", g["requests_processing"])
+        emit("requests_deferred", "gauge", "Number of requests deferred.", g["requests_deferred"])
+        emit("kv_cache_pages_free", "gauge", "Free pages of the paged KV cache.", g["kv_pages_free"])
+        emit("kv_cache_pages_total", "gauge", "Pages of the paged KV cache.", g["kv_pages_total"])
+        return "\n".join(lines) + "\n"
+
+
+class Scheduler:
+    """Owns the engine; `step()` advances every active slot by one scheduling quantum."""
+
+    def __init__(self, engine, tokenizer: Tokenizer, n_batch: int | None = None, log: Callable[[str], None] | None = None):
+        self.eng, self.tok = engine, tokenizer
+        self.n_slots = engine.max_seqs
+        self.n_batch = min(n_batch or engine.max_tokens, engine.max_tokens)
+        self.slots = [Slot(i) for i in range(self.n_slots)]
+        self.queue: deque[Request] = deque()
+        self.lock = threading.Lock()
+        self.wake = threading.Condition(self.lock)
+        self.metrics = Metrics()
+        self.metrics.g["kv_pages_total"] = engine.kv.n_pages
+        self._ids = itertools.count(1)
+        self._stop = False
+        self._thread: threading.Thread | None = None
+        self.log = log or (lambda s: None)
+
+    # ---- submission -------------------------------------------------------------------------------
+    def submit(self, req: Request) -> Request:
+        req.id = next(self._ids)
+        req.t_submit = time.time()
+        if isinstance(req.prompt, str):
+            req.prompt_ids = self.tok.encode(req.prompt)
+        else:
+            req.prompt_ids = list(req.prompt)
+        if not req.prompt_ids:
+            req.prompt_ids = [self.tok.bos_id]
+        limit = self.eng.n_ctx - 1
+        if len(req.prompt_ids) > limit:  # keep the tail, like the reference's prompt truncation
+            req.prompt_ids = req.prompt_ids[:1] + req.prompt_ids[-(limit - 1):]
+        with self.wake:
+            self.queue.append(req)
+            self.metrics.add(requests_total=1)
+            self.metrics.g["requests_deferred"] = len(self.queue)
+            self.wake.notify_all()
+        return req
+
+    def cancel(self, req: Request):
+        req.cancelled = True
+
+    # ---- slot selection with prompt-prefix reuse --------------------------------------------------------
+    @staticmethod
+    def _lcp(a: list[int], b: list[int]) -> int:
+        n = 0
+        for x, y in zip(a, b):
+            if x != y:
+                break
+            n += 1
+        return n
+
+    def _pick_slot(self, req: Request) -> Slot | None:
+        idle = [s for s in self.slots if s.state == SlotState.IDLE]
+        if not idle:
+            return None
+        if req.cache_prompt:
+            best = max(idle, key=lambda s: (self._lcp(s.cache_tokens, req.prompt_ids), -s.t_last_used))
+            if self._lcp(best.cache_tokens, req.prompt_ids) > 0:
+                return best
+        return min(idle, key=lambda s: (len(s.cache_tokens) > 0, s.t_last_used))  # prefer empty, then least recently used
+
+    def _launch(self, slot: Slot, req: Request):
+        eng = self.eng
+        if slot.sid is None:
+            slot.sid = eng.alloc_seq()
+        keep = self._lcp(slot.cache_tokens, req.prompt_ids) if req.cache_prompt else 0
+        keep = min(keep, len(req.prompt_ids) - 1)  # always evaluate at least the last prompt token
+        eng.truncate_seq(slot.sid, keep)
+        slot.cache_tokens = slot.cache_tokens[:keep]
+        slot.n_past = keep
+        slot.req, slot.state = req, SlotState.PROMPT
+        slot.sampler = Sampler(req.sampling)
+        slot.decoder = StreamDecoder(self.tok)
+        req.n_prompt_cached = keep
+        req.t_start = time.time()
+        self._emit(req, "log", f"slot {slot.idx}: request {req.id} | prompt {len(req.prompt_ids)} tokens, "
+                               f"{keep} reused from cache, n_predict {req.n_predict}\n")
+
+    def _emit(self, req: Request, kind: str, content: str):
+        if req.on_event is not None:
+            try:
+                req.on_event(kind, content)
+            except Exception:  # a broken consumer must not take the engine down
+                req.cancelled = True
+
+    # ---- one scheduling quantum ----------------------------------------------------------------------
+    @torch.no_grad()
+    def step(self) -> bool:
+        """Returns False when there was nothing to do."""
+        with self.lock:
+            while self.queue:
+                slot = self._pick_slot(self.queue[0])
+                if slot is None:
+                    break
+                self._launch(slot, self.queue.popleft())
+            self.metrics.g["requests_deferred"] = len(self.queue)
+        active = [s for s in self.slots if s.state != SlotState.IDLE]
+        self.metrics.g["requests_processing"] = len(active)
+        self.metrics.g["kv_pages_free"] = len(self.eng.kv.free)
+        if not active:
+            return False
+        # 1) prompt chunks, sharing the n_batch budget
+        budget = self.n_batch
+        for s in active:
+            if s.state != SlotState.PROMPT or budget <= 0:
+                continue
+            req = s.req
+            if req.cancelled:
+                self._finish(s, "cancelled")
+                continue
+            remaining = req.prompt_ids[s.n_past:]
+            chunk = remaining[:budget]
+            t0 = time.time()
+            try:
+                logits = self.eng.prefill(s.sid, chunk)
+            except RuntimeError as e:
+                self._fail(s, str(e))
+                continue
+            budget -= len(chunk)
+            s.n_past += len(chunk)
+            s.cache_tokens.extend(chunk)
+            req.n_prompt_processed += len(chunk)
+            self.metrics.add(prompt_tokens_total=len(chunk), n_tokens_max=0)
+            self.metrics.c["n_tokens_max"] = max(self.metrics.c["n_tokens_max"], len(chunk))
+            if s.n_past == len(req.prompt_ids):  # prompt complete: sample the first token from its logits
+                tok = self._sample_rows(logits[None], [s])[0]
+                self.metrics.add(prompt_seconds_total=time.time() - req.t_start)
+                req.t_first_token = time.time()
+                s.state = SlotState.GENERATING
+                self._accept(s, tok)
+            else:
+                self.metrics.add(prompt_seconds_total=0.0)
+            _ = t0
+        # 2) one decode token for every generating slot (single batched step)
+        gen = [s for s in self.slots if s.state == SlotState.GENERATING]
+        if gen:
+            for s in list(gen):
+                if s.req.cancelled:
+                    self._finish(s, "cancelled")
+                    gen.remove(s)
+            if gen:
+                t0 = time.time()
+                sids = [s.sid for s in gen]
+                toks = torch.tensor([s.next_token for s in gen], dtype=torch.int32)
+                try:
+                    device_sampling = all(self._device_samplable(s) for s in gen) and self._same_params(gen)
+                    if device_sampling:
+                        p = gen[0].req.sampling
+                        self.eng.sampling = dict(top_k=p.top_k, top_p=p.top_p, min_p=p.min_p, temp=p.temperature, seed=p.seed)
+                        out = self.eng.decode(sids, toks, sample=True)
+                        new = out.cpu().tolist()
+                        for s in gen:
+                            s.sampler.accept(s.next_token)
+                    else:
+                        logits = self.eng.decode(sids, toks, sample=False)
+                        new = self._sample_rows(logits, gen)
+                except RuntimeError as e:
+                    for s in gen:
+                        self._fail(s, str(e))
+                    return True
+                dt = time.time() - t0
+                self.metrics.add(n_decode_total=1, n_busy_slots_total=len(gen), tokens_predicted_total=len(gen),
+                                 tokens_predicted_seconds_total=dt)
+                for s, t in zip(gen, new):
+                    s.cache_tokens.append(s.next_token)
+                    s.n_past += 1
+                    self._accept(s, int(t))
+        return True
+
+    def _device_samplable(self, s: Slot) -> bool:
+        p = s.req.sampling
+        return (p.repeat_penalty == 1.0 and p.frequency_penalty == 0.0 and p.presence_penalty == 0.0 and not p.logit_bias
+                and p.typical_p >= 1.0 and self.eng.device.type == "cuda")
+
+    @staticmethod
+    def _same_params(slots: list[Slot]) -> bool:
+        p0 = slots[0].req.sampling
+        key = (p0.temperature, p0.top_k, p0.top_p, p0.min_p, p0.seed)
+        return all((s.req.sampling.temperature, s.req.sampling.top_k, s.req.sampling.top_p, s.req.sampling.min_p,
+                    s.req.sampling.seed) == key for s in slots)
+
+    def _sample_rows(self, logits: torch.Tensor, slots: list[Slot]) -> list[int]:
+        rows = logits.float().cpu()
+        return [s.sampler.sample(rows[i]) for i, s in enumerate(slots)]
+
+    # ---- token acceptance / completion -------------------------------------------------------------------
+    def _accept(self, s: Slot, tok: int):
+        req = s.req
+        req.output_ids.append(tok)
+        s.next_token = tok
+        is_stop = tok in self.tok.stop_ids and not req.ignore_eos
+        if not is_stop:
+            piece = s.decoder.push(tok)
+            if piece:
+                req.text += piece
+                hit = next((st for st in req.stop if st and st in req.text), None)
+                if hit is not None:
+                    cut = req.text.index(hit)
+                    emitted = len(req.text) - len(piece)
+                    if cut > emitted:
+                        self._emit(req, "token", req.text[emitted:cut])
+                    req.text = req.text[:cut]
+                    self._finish(s, "stop")
+                    return
+                self._emit(req, "token", piece)
+        if is_stop:
+            req.output_ids.pop()
+            self._finish(s, "stop")
+        elif len(req.output_ids) >= req.n_predict:
+            self._finish(s, "length")
+        elif s.n_past + 1 >= self.eng.n_ctx:
+            self._finish(s, "length")  # context full (the reference stops as well unless --context-shift)
+
+    def _finish(self, s: Slot, reason: str):
+        req = s.req
+        tail = s.decoder.flush() if s.decoder else ""
+        if tail and reason != "cancelled":
+            req.text += tail
+            self._emit(req, "token", tail)
+        req.finish_reason = reason
+        req.t_done = time.time()
+        t = req.timings()
+        self._emit(req, "log", f"slot {s.idx}: request {req.id} done ({reason}) | prompt eval {t['prompt_n']} tok "
+                               f"{t['prompt_per_second']} tok/s | eval {t['predicted_n']} tok {t['predicted_per_second']} tok/s\n")
+        self._emit(req, "done", reason)
+        s.state, s.req, s.t_last_used = SlotState.IDLE, None, time.time()
+        if not req.cache_prompt:
+            self.eng.truncate_seq(s.sid, 0)
+            s.cache_tokens, s.n_past = [], 0
+        req.done.set()
+
+    def _fail(self, s: Slot, msg: str):
+        req = s.req
+        self.metrics.add(requests_failed_total=1)
+        req.finish_reason = "error"
+        req.t_done = time.time()
+        self._emit(req, "error", msg)
+        self._emit(req, "done", "error")
+        try:
+            self.eng.truncate_seq(s.sid, 0)
+        except Exception:
+            pass
+        s.state, s.req, s.cache_tokens, s.n_past = SlotState.IDLE, None, [], 0
+        req.done.set()
+
+    # ---- background loop --------------------------------------------------------------------------------
+    def start(self):
+        self._thread = threading.Thread(target=self._loop, name="dlp-scheduler", daemon=True)
+        self._thread.start()
+
+    def stop(self):
+        self._stop = True
+        with self.wake:
+            self.wake.notify_all()
+        if self._thread:
+            self._thread.join(timeout=5)
+
+    def _loop(self):
+        if self.eng.device.type == "cuda":
+            torch.cuda.set_device(self.eng.device)
+        while not self._stop:
+            if not self.step():
+                with self.wake:
+                    if not self.queue and not self._stop:
+                        self.wake.wait(timeout=0.05)
+
+    # ---- blocking convenience ------------------------------------------------------------------------------
+    def generate(self, prompt, **kw) -> Request:
+        req = self.submit(Request(prompt=prompt, **kw))
+        if self._thread is None:
+            while not req.done.is_set():
+                self.step()
+        else:
+            req.done.wait()
+        return req
+
+    def slots_info(self) -> list[dict]:
+        return [{"id": s.idx, "state": s.state.name.lower(), "n_past": s.n_past, "n_cached": len(s.cache_tokens),
+                 "request": s.req.id if s.req else None} for s in self.slots]

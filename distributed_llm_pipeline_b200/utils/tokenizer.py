@@ -1,0 +1,235 @@
+"""Tokenizers driven by GGUF metadata: SentencePiece-style (`tokenizer.ggml.model = "llama"`) and byte-level BPE
+(`"gpt2"`, incl. the Llama-3 pre-tokenizer).
+
+Parity: `llm_tokenizer_spm` / `llm_tokenizer_bpe` (`llama.cpp/src/llama-vocab.cpp:110,279`), token-type handling and
+byte fallback as in `llama_vocab`; detokenisation mirrors `token_to_piece`.  Own implementation (heap-based bigram
+merging for SPM, rank-based merging for BPE).
+"""
+from __future__ import annotations
+
+import heapq
+from functools import lru_cache
+
+try:
+    import regex as re
+except ImportError:  # pragma: no cover
+    import re
+
+from ..gguf.constants import TokenType
+
+SPM_SPACE = "▁"
+
+GPT2_PAT = r"""'s|'t|'re|'ve|'m|'ll|'d| ?\p{L}+| ?\p{N}+| ?[^\s\p{L}\p{N}]+|\s+(?!\S)|\s+"""
+LLAMA3_PAT = (r"(?i:'s|'t|'re|'ve|'m|'ll|'d)|[^\r\n\p{L}\p{N}]?\p{L}+|\p{N}{1,3}| ?[^\s\p{L}\p{N}]+[\r\n]*|\s*[\r\n]+|"
+              r"\s+(?!\S)|\s+")
+
+
+@lru_cache(maxsize=1)
+def _bytes_to_unicode() -> dict[int, str]:
+    bs = list(range(ord("!"), ord("~") + 1)) + list(range(0xA1, 0xAC + 1)) + list(range(0xAE, 0xFF + 1))
+    cs = bs[:]
+    n = 0
+    for b in range(256):
+        if b not in bs:
+            bs.append(b)
+            cs.append(256 + n)
+            n += 1
+    return {b: chr(c) for b, c in zip(bs, cs)}
+
+
+class Tokenizer:
+    def __init__(self, meta: dict):
+        self.model = meta.get("tokenizer.ggml.model", "llama")
+        self.tokens: list[str] = list(meta["tokenizer.ggml.tokens"])
+        self.n_vocab = len(self.tokens)
+        scores = meta.get("tokenizer.ggml.scores")
+        self.scores = [float(x) for x in scores] if scores is not None else [0.0] * self.n_vocab
+        types = meta.get("tokenizer.ggml.token_type")
+        self.types = [int(x) for x in types] if types is not None else [int(TokenType.NORMAL)] * self.n_vocab
+        self.bos_id = int(meta.get("tokenizer.ggml.bos_token_id", 1))
+        self.eos_id = int(meta.get("tokenizer.ggml.eos_token_id", 2))
+        self.unk_id = int(meta.get("tokenizer.ggml.unknown_token_id", 0))
+        self.eot_id = meta.get("tokenizer.ggml.eot_token_id")
+        self.add_bos = bool(meta.get("tokenizer.ggml.add_bos_token", self.model == "llama"))
+        self.add_space_prefix = bool(meta.get("tokenizer.ggml.add_space_prefix", True))
+        self.tok2id = {t: i for i, t in enumerate(self.tokens)}
+        self.byte_ids: dict[int, int] = {}
+        if self.model == "llama":
+            for b in range(256):
+                tid = self.tok2id.get(f"<0x{b:02X}>")
+                if tid is not None:
+                    self.byte_ids[b] = tid
+        else:
+            merges = meta.get("tokenizer.ggml.merges", [])
+            self.ranks = {tuple(m.split(" ", 1)): i for i, m in enumerate(merges)}
+            pre = meta.get("tokenizer.ggml.pre", "default")
+            self.pat = re.compile(LLAMA3_PAT if pre in ("llama-bpe", "llama3", "llama-v3") else GPT2_PAT)
+            self.b2u = _bytes_to_unicode()
+            self.u2b = {u: b for b, u in self.b2u.items()}
+        self.special = {t: i for i, t in enumerate(self.tokens) if self.types[i] in (TokenType.CONTROL, TokenType.USER_DEFINED) and len(t) > 1}
+        self.stop_ids = {self.eos_id} | ({int(self.eot_id)} if self.eot_id is not None else set())
+
+    @classmethod
+    def from_gguf(cls, src):
+        from ..gguf import open_gguf
+        f = open_gguf(src) if isinstance(src, str) else src
+        return cls(f.metadata)
+
+    # ---- encode -----------------------------------------------------------------------------------
+    def _spm_encode(self, text: str) -> list[int]:
+        if not text:
+            return []
+        syms = list(text)
+        n = len(syms)
+        prev = list(range(-1, n - 1))
+        nxt = list(range(1, n + 1))
+        nxt[-1] = -1
+        alive = [True] * n
+        heap: list = []
+
+        def push(i):
+            j = nxt[i]
+            if i < 0 or j < 0:
+                return
+            piece = syms[i] + syms[j]
+            tid = self.tok2id.get(piece)
+            if tid is not None:
+                heapq.heappush(heap, (-self.scores[tid], i, piece))
+
+        for i in range(n - 1):
+            push(i)
+        while heap:
+            _, i, piece = heapq.heappop(heap)
+            j = nxt[i] if alive[i] else -1
+            if j < 0 or not alive[j] or syms[i] + syms[j] != piece:
+                continue
+            syms[i] = piece
+            alive[j] = False
+            nxt[i] = nxt[j]
+            if nxt[j] >= 0:
+                prev[nxt[j]] = i
+            if prev[i] >= 0:
+                push(prev[i])
+            push(i)
+        out: list[int] = []
+        i = 0
+        while i >= 0:
+            s = syms[i]
+            tid = self.tok2id.get(s)
+            if tid is not None:
+                out.append(tid)
+            else:
+                for b in s.encode("utf-8"):
+                    out.append(self.byte_ids.get(b, self.unk_id))
+            i = nxt[i]
+        return out
+
+    def _bpe_word(self, word: str) -> list[str]:
+        parts = list(word)
+        while len(parts) > 1:
+            best, bi = None, -1
+            for i in range(len(parts) - 1):
+                r = self.ranks.get((parts[i], parts[i + 1]))
+                if r is not None and (best is None or r < best):
+                    best, bi = r, i
+            if best is None:
+                break
+            parts[bi:bi + 2] = [parts[bi] + parts[bi + 1]]
+        return parts
+
+    def _encode_plain(self, text: str) -> list[int]:
+        if self.model == "llama":
+            t = text.replace(" ", SPM_SPACE)
+            return self._spm_encode(t)
+        out: list[int] = []
+        for m in self.pat.findall(text):
+            word = "".join(self.b2u[b] for b in m.encode("utf-8"))
+            for piece in self._bpe_word(word):
+                tid = self.tok2id.get(piece)
+                if tid is not None:
+                    out.append(tid)
+                else:
+                    out.extend(self.tok2id.get(ch, self.unk_id) for ch in piece)
+        return out
+
+    def encode(self, text: str, add_bos: bool | None = None, parse_special: bool = True) -> list[int]:
+        ids: list[int] = []
+        if add_bos if add_bos is not None else self.add_bos:
+            ids.append(self.bos_id)
+        segments: list[tuple[str, bool]] = [(text, False)]
+        if parse_special and self.special:
+            pat = re.compile("|".join(re.escape(t) for t in sorted(self.special, key=len, reverse=True)))
+            segments, last = [], 0
+            for m in pat.finditer(text):
+                if m.start() > last:
+                    segments.append((text[last:m.start()], False))
+                segments.append((m.group(0), True))
+                last = m.end()
+            if last < len(text):
+                segments.append((text[last:], False))
+        first = True
+        for seg, is_special in segments:
+            if is_special:
+                ids.append(self.special[seg])
+            else:
+                if self.model == "llama" and first and self.add_space_prefix:
+                    seg = " " + seg
+                ids.extend(self._encode_plain(seg))
+            first = False
+        return ids
+
+    # ---- decode -----------------------------------------------------------------------------------
+    def token_bytes(self, tid: int) -> bytes:
+        if tid < 0 or tid >= self.n_vocab:
+            return b""
+        t, typ = self.tokens[tid], self.types[tid]
+        if typ == TokenType.CONTROL:
+            return b""
+        if self.model == "llama":
+            if typ == TokenType.BYTE:
+                return bytes([int(t[3:5], 16)])
+            return t.replace(SPM_SPACE, " ").encode("utf-8")
+        return bytes(self.u2b.get(ch, ord("?")) for ch in t)
+
+    def decode(self, ids: list[int], strip_leading_space: bool = True) -> str:
+        data = b"".join(self.token_bytes(i) for i in ids)
+        s = data.decode("utf-8", errors="replace")
+        if self.model == "llama" and strip_leading_space and self.add_space_prefix and s.startswith(" "):
+            s = s[1:]
+        return s
+
+
+class StreamDecoder:
+    """Incremental detokeniser: holds back incomplete UTF-8 sequences so a multi-byte character is never split
+    across stream events (the reference's 64-byte stdout chunks + from_utf8_lossy produce U+FFFD there,
+    `orchestrator/src/main.rs:86-90`)."""
+
+    def __init__(self, tok: Tokenizer):
+        self.tok = tok
+        self.pending = b""
+        self.first = True
+
+    def push(self, tid: int) -> str:
+        self.pending += self.tok.token_bytes(tid)
+        cut = len(self.pending)
+        # find the longest prefix that is valid UTF-8
+        for back in range(1, min(4, len(self.pending)) + 1):
+            b = self.pending[-back]
+            if b & 0xC0 == 0x80:
+                continue
+            need = 1 if b < 0x80 else 2 if b >> 5 == 0b110 else 3 if b >> 4 == 0b1110 else 4 if b >> 3 == 0b11110 else 1
+            if need > back:
+                cut = len(self.pending) - back
+            break
+        out, self.pending = self.pending[:cut], self.pending[cut:]
+        s = out.decode("utf-8", errors="replace")
+        if self.first and s:
+            if self.tok.model == "llama" and self.tok.add_space_prefix and s.startswith(" "):
+                s = s[1:]
+            self.first = False
+        return s
+
+    def flush(self) -> str:
+        s = self.pending.decode("utf-8", errors="replace")
+        self.pending = b""
+        return s

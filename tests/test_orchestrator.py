@@ -1,0 +1,159 @@
+"""Wire-level tests of the /chat SSE API against the reference's format (`orchestrator/src/main.rs:18-27,97,100-111`):
+real sockets, real tiny model on CPU, no mocks (the reference's server tests work the same way)."""
+import asyncio
+import json
+import socket
+import threading
+import time
+
+import pytest
+
+from distributed_llm_pipeline_b200.serving.orchestrator import Orchestrator, build_service, sse_event
+from distributed_llm_pipeline_b200.serving.scheduler import Request
+from distributed_llm_pipeline_b200.serving.sampler import SamplingParams
+from distributed_llm_pipeline_b200.utils.tokenizer import StreamDecoder, Tokenizer
+
+
+@pytest.fixture(scope="module")
+def server(tmp_models):
+    sched, info, logs = build_service(tmp_models[("tiny", "F16")], device="cpu", n_ctx=128, n_slots=2, n_batch=32)
+    sched.start()
+    orch = Orchestrator(sched, info, n_predict=12, startup_logs=logs)
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    port = s.getsockname()[1]
+    s.close()
+    loop = asyncio.new_event_loop()
+    t = threading.Thread(target=lambda: loop.run_until_complete(orch.serve("127.0.0.1", port)), daemon=True)
+    t.start()
+    for _ in range(100):
+        try:
+            socket.create_connection(("127.0.0.1", port), timeout=0.2).close()
+            break
+        except OSError:
+            time.sleep(0.05)
+    yield port, sched
+    sched.stop()
+
+
+def _http(port, method, path, body=b"", headers=None, read_all=True):
+    s = socket.create_connection(("127.0.0.1", port), timeout=30)
+    h = {"Host": "x", "Content-Length": str(len(body)), "Connection": "close"}
+    h.update(headers or {})
+    s.sendall((f"{method} {path} HTTP/1.1\r\n" + "".join(f"{k}: {v}\r\n" for k, v in h.items()) + "\r\n").encode() + body)
+    data = b""
+    while True:
+        chunk = s.recv(65536)
+        if not chunk:
+            break
+        data += chunk
+    s.close()
+    head, _, payload = data.partition(b"\r\n\r\n")
+    lines = head.decode().split("\r\n")
+    hdrs = {l.split(":", 1)[0].lower(): l.split(":", 1)[1].strip() for l in lines[1:] if ":" in l}
+    return lines[0], hdrs, payload
+
+
+def test_event_wire_format_matches_reference_serialisation():
+    # serde_json of StreamMessage{msg_type, content}: field order, compact separators, UTF-8 kept verbatim
+    assert sse_event("token", "hé\n") == 'data: {"msg_type":"token","content":"hé\\n"}\n\n'.encode()
+
+
+def test_chat_streams_log_and_token_events(server):
+    port, _ = server
+    status, hdrs, payload = _http(port, "POST", "/chat", json.dumps({"prompt": "Once upon a time"}).encode(),
+                                  {"Content-Type": "application/json"})
+    assert status.startswith("HTTP/1.1 200")
+    assert hdrs["content-type"] == "text/event-stream" and hdrs["cache-control"] == "no-cache"
+    assert hdrs["access-control-allow-origin"] == "*"
+    events = []
+    for block in payload.decode().split("\n\n"):
+        if block.startswith("data: "):
+            events.append(json.loads(block[6:]))
+        else:
+            assert block == "" or block.startswith(":")     # keep-alive comments only
+    kinds = {e["msg_type"] for e in events}
+    assert kinds == {"log", "token"}
+    assert all(set(e) == {"msg_type", "content"} for e in events)
+    assert any("offloaded" in e["content"] for e in events if e["msg_type"] == "log")   # the UI's highlight hook
+    assert sum(e["msg_type"] == "token" for e in events) >= 1
+
+
+def test_chat_rejects_bad_body_and_serves_static_and_cors(server):
+    port, _ = server
+    status, _, _ = _http(port, "POST", "/chat", b'{"nope": 1}', {"Content-Type": "application/json"})
+    assert "422" in status
+    status, hdrs, body = _http(port, "GET", "/")
+    assert status.startswith("HTTP/1.1 200") and b"/chat" in body and hdrs["content-type"].startswith("text/html")
+    status, _, _ = _http(port, "GET", "/../../etc/passwd")
+    assert "404" in status
+    status, hdrs, _ = _http(port, "OPTIONS", "/chat", headers={"Origin": "http://x", "Access-Control-Request-Method": "POST"})
+    assert status.startswith("HTTP/1.1 200") and hdrs["access-control-allow-origin"] == "*"
+
+
+def test_aux_routes(server):
+    port, sched = server
+    _, _, body = _http(port, "GET", "/health")
+    assert json.loads(body)["status"] == "ok"
+    _, _, body = _http(port, "POST", "/completion", json.dumps({"prompt": "a b c", "n_predict": 5, "temperature": 0}).encode())
+    d = json.loads(body)
+    assert d["tokens_predicted"] <= 5 and "timings" in d and d["stop"] is True
+    _, _, body = _http(port, "POST", "/v1/chat/completions",
+                       json.dumps({"messages": [{"role": "user", "content": "hi"}], "max_tokens": 4, "temperature": 0}).encode())
+    d = json.loads(body)
+    assert d["object"] == "chat.completion" and d["usage"]["completion_tokens"] <= 4
+    _, _, body = _http(port, "GET", "/metrics")
+    text = body.decode()
+    assert "llamacpp:prompt_tokens_total" in text and "llamacpp:tokens_predicted_total" in text
+    _, _, body = _http(port, "GET", "/slots")
+    assert len(json.loads(body)) == sched.n_slots
+    _, _, body = _http(port, "POST", "/tokenize", json.dumps({"content": "hello world"}).encode())
+    toks = json.loads(body)["tokens"]
+    _, _, body = _http(port, "POST", "/detokenize", json.dumps({"tokens": toks}).encode())
+    assert json.loads(body)["content"].strip() == "hello world"
+
+
+def test_concurrent_requests_share_slots_and_queue(server):
+    port, sched = server
+    results = []
+
+    def one(i):
+        _, _, body = _http(port, "POST", "/completion", json.dumps({"prompt": f"request {i}", "n_predict": 6, "temperature": 0}).encode())
+        results.append(json.loads(body))
+
+    ts = [threading.Thread(target=one, args=(i,)) for i in range(5)]     # 5 requests, 2 slots -> 3 deferred
+    [t.start() for t in ts]
+    [t.join(60) for t in ts]
+    assert len(results) == 5 and all(r["stop"] for r in results)
+
+
+def test_greedy_is_deterministic_and_prefix_cache_is_used(server):
+    _, sched = server
+    p = "the quick brown fox jumps over the lazy dog"
+    a = sched.generate(p, n_predict=8, sampling=SamplingParams(temperature=0.0))
+    b = sched.generate(p, n_predict=8, sampling=SamplingParams(temperature=0.0))
+    assert a.output_ids == b.output_ids
+    assert b.n_prompt_cached > 0 and b.n_prompt_processed < len(b.prompt_ids)      # LCP reuse
+
+
+def test_tokenizer_roundtrip_and_stream_decoder(tmp_models):
+    tok = Tokenizer.from_gguf(tmp_models[("tiny", "F16")])
+    for text in ["hello world", "a  b", "naïve café ☕", "line1\nline2"]:
+        ids = tok.encode(text)
+        assert ids[0] == tok.bos_id
+        assert tok.decode(ids[1:]) == text
+    ids = tok.encode("☕ok", add_bos=False)   # multi-byte char goes through byte tokens in the synthetic vocab
+    sd = StreamDecoder(tok)
+    pieces = [sd.push(i) for i in ids]
+    assert "�" not in "".join(pieces) and "".join(pieces) + sd.flush() == "☕ok"
+
+
+def test_stop_string_and_n_predict(server):
+    _, sched = server
+    r = sched.generate("abc", n_predict=3, sampling=SamplingParams(temperature=0.0))
+    assert len(r.output_ids) <= 3 and r.finish_reason in ("length", "stop")
+    full = sched.generate("abc", n_predict=10, sampling=SamplingParams(temperature=0.0), cache_prompt=False)
+    if len(full.text) > 3:
+        needle = full.text[2:4]
+        cut = sched.generate("abc", n_predict=10, sampling=SamplingParams(temperature=0.0), stop=[needle])
+        assert needle not in cut.text and cut.finish_reason == "stop"
