@@ -1,0 +1,480 @@
+// dlp-worker: native CPU pipeline-stage worker (BASELINE config 1: layer-split pipeline over localhost TCP workers).
+//
+// Reference counterpart: `rpc-server` + the ggml-RPC backend (llama.cpp/tools/rpc/rpc-server.cpp, ggml/src/ggml-rpc/
+// ggml-rpc.cpp).  There the client owns the graph and the weights: it uploads every tensor (SET_TENSOR), serialises
+// the compute graph per step (GRAPH_COMPUTE) and moves activations worker -> client -> worker (two TCP hops).  This
+// worker is a different design with the same capability:
+//   * it memory-maps the GGUF file itself and owns layers [l0, l1) (+ embedding on the first, norm + lm_head on the
+//     last stage) - no weights ever cross the socket;
+//   * the wire carries only token ids / hidden states in and hidden states / logits out, per call:
+//       request : u8 cmd | u32 seq | u32 n_tokens | u32 pos0 | u32 flags | u64 nbytes | payload
+//       response: u32 status | u64 nbytes | payload
+//     cmds: 1 HELLO (-> info), 2 RUN, 3 RESET seq, 4 TRUNCATE seq to pos0, 5 SHUTDOWN;
+//   * it keeps a per-sequence KV cache for its layers and validates every size it is given.
+// Kernels: fp32 accumulate over on-the-fly decoded F32/F16/Q8_0/Q4_K/Q5_K/Q6_K rows (bit layouts: the GGUF contract,
+// ggml-common.h:170-336), OpenMP over output rows.
+//
+// Build: g++ -O3 -std=c++17 -fopenmp -mavx2 -mfma -mf16c worker.cpp -o dlp-worker
+#include <arpa/inet.h>
+#include <fcntl.h>
+#include <immintrin.h>
+#include <netinet/in.h>
+#include <netinet/tcp.h>
+#include <signal.h>
+#include <sys/mman.h>
+#include <sys/socket.h>
+#include <sys/stat.h>
+#include <unistd.h>
+
+#include <cmath>
+#include <cstdint>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <map>
+#include <stdexcept>
+#include <string>
+#include <vector>
+
+namespace {
+
+constexpr uint32_t PROTO_VERSION = 1;
+enum Cmd : uint8_t { HELLO = 1, RUN = 2, RESET = 3, TRUNCATE = 4, SHUTDOWN = 5 };
+enum GType : uint32_t { T_F32 = 0, T_F16 = 1, T_Q8_0 = 8, T_Q4_K = 12, T_Q5_K = 13, T_Q6_K = 14, T_BF16 = 30 };
+
+// ---- GGUF -----------------------------------------------------------------------------------------------------------
+struct Tensor {
+    std::vector<uint64_t> ne;  // innermost first
+    uint32_t type = 0;
+    const uint8_t* data = nullptr;
+    uint64_t rows() const { uint64_t r = 1; for (size_t i = 1; i < ne.size(); ++i) r *= ne[i]; return r; }
+    uint64_t cols() const { return ne.empty() ? 0 : ne[0]; }
+};
+
+size_t row_bytes(uint32_t type, uint64_t k) {
+    switch (type) {
+        case T_F32: return k * 4;
+        case T_F16: case T_BF16: return k * 2;
+        case T_Q8_0: return k / 32 * 34;
+        case T_Q4_K: return k / 256 * 144;
+        case T_Q5_K: return k / 256 * 176;
+        case T_Q6_K: return k / 256 * 210;
+        default: throw std::runtime_error("unsupported tensor type " + std::to_string(type));
+    }
+}
+
+struct Gguf {
+    const uint8_t* base = nullptr;
+    size_t size = 0;
+    std::map<std::string, double> num;
+    std::map<std::string, std::string> str;
+    std::map<std::string, uint64_t> arr_len;
+    std::map<std::string, Tensor> tensors;
+
+    struct Cur {
+        const uint8_t* p; const uint8_t* end;
+        template <typename T> T get() { if (p + sizeof(T) > end) throw std::runtime_error("gguf: truncated"); T v; memcpy(&v, p, sizeof(T)); p += sizeof(T); return v; }
+        std::string s() { uint64_t n = get<uint64_t>(); if (p + n > end) throw std::runtime_error("gguf: truncated string"); std::string r((const char*)p, n); p += n; return r; }
+    };
+    static size_t scalar_size(uint32_t t) { static const size_t sz[13] = {1, 1, 2, 2, 4, 4, 4, 1, 0, 0, 8, 8, 8}; return t < 13 ? sz[t] : 0; }
+
+    void skip_or_read(Cur& c, uint32_t t, const std::string& key) {
+        if (t == 8) { str[key] = c.s(); return; }
+        if (t == 9) {
+            uint32_t et = c.get<uint32_t>(); uint64_t n = c.get<uint64_t>();
+            arr_len[key] = n;
+            if (et == 8) { for (uint64_t i = 0; i < n; ++i) c.s(); }
+            else { size_t s = scalar_size(et); if (!s) throw std::runtime_error("gguf: nested arrays unsupported"); if (c.p + s * n > c.end) throw std::runtime_error("gguf: truncated array"); c.p += s * n; }
+            return;
+        }
+        double v = 0;
+        switch (t) {
+            case 0: v = c.get<uint8_t>(); break;  case 1: v = c.get<int8_t>(); break;
+            case 2: v = c.get<uint16_t>(); break; case 3: v = c.get<int16_t>(); break;
+            case 4: v = c.get<uint32_t>(); break; case 5: v = c.get<int32_t>(); break;
+            case 6: v = c.get<float>(); break;    case 7: v = c.get<uint8_t>(); break;
+            case 10: v = (double)c.get<uint64_t>(); break; case 11: v = (double)c.get<int64_t>(); break;
+            case 12: v = c.get<double>(); break;
+            default: throw std::runtime_error("gguf: bad value type");
+        }
+        num[key] = v;
+    }
+
+    void open(const std::string& path) {
+        int fd = ::open(path.c_str(), O_RDONLY);
+        if (fd < 0) throw std::runtime_error("cannot open " + path);
+        struct stat st{};
+        fstat(fd, &st);
+        size = (size_t)st.st_size;
+        base = (const uint8_t*)mmap(nullptr, size, PROT_READ, MAP_SHARED, fd, 0);
+        ::close(fd);
+        if (base == MAP_FAILED) throw std::runtime_error("mmap failed");
+        Cur c{base, base + size};
+        if (c.get<uint32_t>() != 0x46554747u) throw std::runtime_error("not a GGUF file");
+        uint32_t ver = c.get<uint32_t>();
+        if (ver != 2 && ver != 3) throw std::runtime_error("unsupported GGUF version");
+        uint64_t nt = c.get<uint64_t>(), nkv = c.get<uint64_t>();
+        for (uint64_t i = 0; i < nkv; ++i) { std::string k = c.s(); uint32_t t = c.get<uint32_t>(); skip_or_read(c, t, k); }
+        struct Info { std::string name; Tensor t; uint64_t off; };
+        std::vector<Info> infos;
+        for (uint64_t i = 0; i < nt; ++i) {
+            Info in; in.name = c.s();
+            uint32_t nd = c.get<uint32_t>();
+            for (uint32_t d = 0; d < nd; ++d) in.t.ne.push_back(c.get<uint64_t>());
+            in.t.type = c.get<uint32_t>(); in.off = c.get<uint64_t>();
+            infos.push_back(in);
+        }
+        uint64_t align = num.count("general.alignment") ? (uint64_t)num["general.alignment"] : 32;
+        uint64_t data_off = ((uint64_t)(c.p - base) + align - 1) / align * align;
+        for (auto& in : infos) {
+            in.t.data = base + data_off + in.off;
+            tensors[in.name] = in.t;
+        }
+    }
+    const Tensor& get(const std::string& n) const { auto it = tensors.find(n); if (it == tensors.end()) throw std::runtime_error("missing tensor " + n); return it->second; }
+    bool has(const std::string& n) const { return tensors.count(n) > 0; }
+    double n(const std::string& k, double d) const { auto it = num.find(k); return it == num.end() ? d : it->second; }
+};
+
+// ---- row decoding ----------------------------------------------------------------------------------------------------
+inline float f16(uint16_t h) { return _cvtsh_ss(h); }
+
+inline void scale_min_k4(int j, const uint8_t* q, int& d, int& m) {
+    if (j < 4) { d = q[j] & 63; m = q[j + 4] & 63; }
+    else { d = (q[j + 4] & 0xF) | ((q[j - 4] >> 6) << 4); m = (q[j + 4] >> 4) | ((q[j] >> 6) << 4); }
+}
+
+void decode_row(uint32_t type, const uint8_t* src, uint64_t k, float* out) {
+    switch (type) {
+        case T_F32: memcpy(out, src, k * 4); break;
+        case T_F16: { const uint16_t* h = (const uint16_t*)src; for (uint64_t i = 0; i < k; ++i) out[i] = f16(h[i]); break; }
+        case T_BF16: { const uint16_t* h = (const uint16_t*)src; for (uint64_t i = 0; i < k; ++i) { uint32_t u = (uint32_t)h[i] << 16; memcpy(out + i, &u, 4); } break; }
+        case T_Q8_0:
+            for (uint64_t b = 0; b < k / 32; ++b) {
+                const uint8_t* p = src + b * 34;
+                uint16_t dh; memcpy(&dh, p, 2);
+                const float d = f16(dh);
+                const int8_t* q = (const int8_t*)(p + 2);
+                for (int i = 0; i < 32; ++i) out[b * 32 + i] = d * q[i];
+            }
+            break;
+        case T_Q4_K:
+            for (uint64_t b = 0; b < k / 256; ++b) {
+                const uint8_t* p = src + b * 144;
+                uint16_t dh, mh; memcpy(&dh, p, 2); memcpy(&mh, p + 2, 2);
+                const float d = f16(dh), dm = f16(mh);
+                const uint8_t* sc = p + 4; const uint8_t* q = p + 16;
+                float* y = out + b * 256;
+                for (int j = 0; j < 4; ++j) {
+                    int s1, m1, s2, m2;
+                    scale_min_k4(2 * j, sc, s1, m1); scale_min_k4(2 * j + 1, sc, s2, m2);
+                    for (int l = 0; l < 32; ++l) { y[l] = d * s1 * (q[l] & 0xF) - dm * m1; y[l + 32] = d * s2 * (q[l] >> 4) - dm * m2; }
+                    y += 64; q += 32;
+                }
+            }
+            break;
+        case T_Q5_K:
+            for (uint64_t b = 0; b < k / 256; ++b) {
+                const uint8_t* p = src + b * 176;
+                uint16_t dh, mh; memcpy(&dh, p, 2); memcpy(&mh, p + 2, 2);
+                const float d = f16(dh), dm = f16(mh);
+                const uint8_t* sc = p + 4; const uint8_t* qh = p + 16; const uint8_t* q = p + 48;
+                float* y = out + b * 256;
+                for (int j = 0; j < 4; ++j) {
+                    int s1, m1, s2, m2;
+                    scale_min_k4(2 * j, sc, s1, m1); scale_min_k4(2 * j + 1, sc, s2, m2);
+                    for (int l = 0; l < 32; ++l) {
+                        y[l] = d * s1 * ((q[l] & 0xF) + (((qh[l] >> (2 * j)) & 1) << 4)) - dm * m1;
+                        y[l + 32] = d * s2 * ((q[l] >> 4) + (((qh[l] >> (2 * j + 1)) & 1) << 4)) - dm * m2;
+                    }
+                    y += 64; q += 32;
+                }
+            }
+            break;
+        case T_Q6_K:
+            for (uint64_t b = 0; b < k / 256; ++b) {
+                const uint8_t* p = src + b * 210;
+                const uint8_t* ql = p; const uint8_t* qh = p + 128; const int8_t* sc = (const int8_t*)(p + 192);
+                uint16_t dh; memcpy(&dh, p + 208, 2);
+                const float d = f16(dh);
+                float* y = out + b * 256;
+                for (int half = 0; half < 2; ++half) {
+                    for (int l = 0; l < 32; ++l) {
+                        const int is = l / 16;
+                        const int q1 = (int)((ql[l] & 0xF) | (((qh[l] >> 0) & 3) << 4)) - 32;
+                        const int q2 = (int)((ql[l + 32] & 0xF) | (((qh[l] >> 2) & 3) << 4)) - 32;
+                        const int q3 = (int)((ql[l] >> 4) | (((qh[l] >> 4) & 3) << 4)) - 32;
+                        const int q4 = (int)((ql[l + 32] >> 4) | (((qh[l] >> 6) & 3) << 4)) - 32;
+                        y[l] = d * sc[is] * q1; y[l + 32] = d * sc[is + 2] * q2; y[l + 64] = d * sc[is + 4] * q3; y[l + 96] = d * sc[is + 6] * q4;
+                    }
+                    y += 128; ql += 64; qh += 32; sc += 8;
+                }
+            }
+            break;
+        default: throw std::runtime_error("decode_row: unsupported type");
+    }
+}
+
+inline float dot(const float* a, const float* b, uint64_t n) {
+    __m256 acc0 = _mm256_setzero_ps(), acc1 = _mm256_setzero_ps();
+    uint64_t i = 0;
+    for (; i + 16 <= n; i += 16) {
+        acc0 = _mm256_fmadd_ps(_mm256_loadu_ps(a + i), _mm256_loadu_ps(b + i), acc0);
+        acc1 = _mm256_fmadd_ps(_mm256_loadu_ps(a + i + 8), _mm256_loadu_ps(b + i + 8), acc1);
+    }
+    acc0 = _mm256_add_ps(acc0, acc1);
+    __m128 s = _mm_add_ps(_mm256_castps256_ps128(acc0), _mm256_extractf128_ps(acc0, 1));
+    s = _mm_hadd_ps(s, s); s = _mm_hadd_ps(s, s);
+    float r = _mm_cvtss_f32(s);
+    for (; i < n; ++i) r += a[i] * b[i];
+    return r;
+}
+
+// y[T][N] = x[T][K] . W[N][K]^T     (W decoded row by row, shared across the T tokens)
+void matmul(const Tensor& w, const float* x, int T, float* y, bool accumulate = false) {
+    const uint64_t K = w.cols(), N = w.rows();
+    const size_t rb = row_bytes(w.type, K);
+#pragma omp parallel
+    {
+        std::vector<float> row(K);
+#pragma omp for schedule(static)
+        for (int64_t n = 0; n < (int64_t)N; ++n) {
+            const float* r;
+            if (w.type == T_F32) r = (const float*)(w.data + n * rb);
+            else { decode_row(w.type, w.data + n * rb, K, row.data()); r = row.data(); }
+            for (int t = 0; t < T; ++t) {
+                const float v = dot(r, x + (size_t)t * K, K);
+                if (accumulate) y[(size_t)t * N + n] += v; else y[(size_t)t * N + n] = v;
+            }
+        }
+    }
+}
+
+void rmsnorm(const float* x, const float* w, float eps, int T, int E, float* out) {
+    for (int t = 0; t < T; ++t) {
+        const float* r = x + (size_t)t * E;
+        double ss = 0;
+        for (int i = 0; i < E; ++i) ss += (double)r[i] * r[i];
+        const float s = 1.0f / std::sqrt((float)(ss / E) + eps);
+        for (int i = 0; i < E; ++i) out[(size_t)t * E + i] = r[i] * s * w[i];
+    }
+}
+
+// ---- model stage ------------------------------------------------------------------------------------------------------
+struct Hparams { int n_embd, n_layer, n_head, n_head_kv, head_dim, n_ff, n_vocab, n_rot, n_ctx; float eps, theta; };
+
+struct SeqCache { std::vector<std::vector<float>> k, v; int len = 0; };  // per local layer: [n_ctx][Hkv*D]
+
+struct Stage {
+    Gguf g;
+    Hparams hp{};
+    int l0 = 0, l1 = 0;
+    bool first = false, last = false;
+    std::vector<float> inv_freq;
+    std::map<uint32_t, SeqCache> seqs;
+
+    void load(const std::string& path, int a, int b, int n_ctx) {
+        g.open(path);
+        const std::string ar = g.str.count("general.architecture") ? g.str["general.architecture"] : "llama";
+        auto N = [&](const char* k, double d) { return g.n(ar + "." + k, d); };
+        hp.n_embd = (int)N("embedding_length", 0); hp.n_layer = (int)N("block_count", 0);
+        hp.n_head = (int)N("attention.head_count", 0); hp.n_head_kv = (int)N("attention.head_count_kv", hp.n_head);
+        hp.head_dim = (int)N("attention.key_length", hp.n_embd / std::max(1, hp.n_head));
+        hp.n_ff = (int)N("feed_forward_length", 0); hp.eps = (float)N("attention.layer_norm_rms_epsilon", 1e-5);
+        hp.theta = (float)N("rope.freq_base", 10000.0); hp.n_rot = (int)N("rope.dimension_count", hp.head_dim);
+        hp.n_vocab = (int)g.get("token_embd.weight").rows();
+        hp.n_ctx = n_ctx;
+        if (N("expert_count", 0) > 0) throw std::runtime_error("MoE checkpoints are not supported by the CPU worker");
+        l0 = a; l1 = b < 0 ? hp.n_layer : b;
+        if (l0 < 0 || l1 > hp.n_layer || l0 >= l1) throw std::runtime_error("bad layer range");
+        first = l0 == 0; last = l1 == hp.n_layer;
+        inv_freq.resize(hp.n_rot / 2);
+        for (int i = 0; i < hp.n_rot / 2; ++i) inv_freq[i] = std::pow(hp.theta, -2.0f * i / hp.n_rot);
+        if (g.has("rope_freqs.weight")) { const float* ff = (const float*)g.get("rope_freqs.weight").data; for (size_t i = 0; i < inv_freq.size(); ++i) inv_freq[i] /= ff[i]; }
+    }
+
+    SeqCache& seq(uint32_t id) {
+        auto it = seqs.find(id);
+        if (it != seqs.end()) return it->second;
+        SeqCache& c = seqs[id];
+        const size_t kv = (size_t)hp.n_head_kv * hp.head_dim;
+        c.k.assign(l1 - l0, std::vector<float>((size_t)hp.n_ctx * kv));
+        c.v.assign(l1 - l0, std::vector<float>((size_t)hp.n_ctx * kv));
+        return c;
+    }
+
+    void rope(float* x, int n_heads, int pos) const {
+        const int D = hp.head_dim;
+        for (int h = 0; h < n_heads; ++h)
+            for (int i = 0; i < hp.n_rot / 2; ++i) {
+                const float a = pos * inv_freq[i], c = std::cos(a), s = std::sin(a);
+                float* p = x + (size_t)h * D + 2 * i;
+                const float x0 = p[0], x1 = p[1];
+                p[0] = x0 * c - x1 * s; p[1] = x0 * s + x1 * c;
+            }
+    }
+
+    // in: token ids (first stage) or hidden [T][E]; out: hidden [T][E] or logits ([1|T][vocab]) on the last stage
+    std::vector<float> run(uint32_t sid, int T, int pos0, uint32_t flags, const uint8_t* payload, size_t nbytes) {
+        const int E = hp.n_embd, D = hp.head_dim, Hq = hp.n_head, Hkv = hp.n_head_kv, F = hp.n_ff;
+        if (T <= 0 || T > hp.n_ctx) throw std::runtime_error("bad token count");
+        SeqCache& c = seq(sid);
+        if (pos0 != c.len) throw std::runtime_error("position " + std::to_string(pos0) + " does not continue sequence of length " + std::to_string(c.len));
+        if (pos0 + T > hp.n_ctx) throw std::runtime_error("context overflow");
+        std::vector<float> h((size_t)T * E);
+        if (first) {
+            if (nbytes != (size_t)T * 4) throw std::runtime_error("payload size mismatch (token ids)");
+            const Tensor& emb = g.get("token_embd.weight");
+            const size_t rb = row_bytes(emb.type, E);
+            for (int t = 0; t < T; ++t) {
+                int32_t id; memcpy(&id, payload + (size_t)t * 4, 4);
+                if (id < 0 || id >= hp.n_vocab) throw std::runtime_error("token id out of range");
+                decode_row(emb.type, emb.data + (size_t)id * rb, E, h.data() + (size_t)t * E);
+            }
+        } else {
+            if (nbytes != (size_t)T * E * 4) throw std::runtime_error("payload size mismatch (hidden states)");
+            memcpy(h.data(), payload, nbytes);
+        }
+        const int qd = Hq * D, kvd = Hkv * D, gqa = Hq / Hkv;
+        std::vector<float> xn((size_t)T * E), q((size_t)T * qd), k((size_t)T * kvd), v((size_t)T * kvd), att((size_t)T * qd),
+            gate((size_t)T * F), up((size_t)T * F);
+        const float scale = 1.0f / std::sqrt((float)D);
+        for (int il = l0; il < l1; ++il) {
+            const std::string p = "blk." + std::to_string(il) + ".";
+            rmsnorm(h.data(), (const float*)g.get(p + "attn_norm.weight").data, hp.eps, T, E, xn.data());
+            matmul(g.get(p + "attn_q.weight"), xn.data(), T, q.data());
+            matmul(g.get(p + "attn_k.weight"), xn.data(), T, k.data());
+            matmul(g.get(p + "attn_v.weight"), xn.data(), T, v.data());
+            std::vector<float>& kc = c.k[il - l0];
+            std::vector<float>& vc = c.v[il - l0];
+            for (int t = 0; t < T; ++t) {
+                rope(q.data() + (size_t)t * qd, Hq, pos0 + t);
+                rope(k.data() + (size_t)t * kvd, Hkv, pos0 + t);
+                memcpy(kc.data() + (size_t)(pos0 + t) * kvd, k.data() + (size_t)t * kvd, kvd * 4);
+                memcpy(vc.data() + (size_t)(pos0 + t) * kvd, v.data() + (size_t)t * kvd, kvd * 4);
+            }
+#pragma omp parallel for collapse(2) schedule(static)
+            for (int t = 0; t < T; ++t)
+                for (int hq = 0; hq < Hq; ++hq) {
+                    const int n_keys = pos0 + t + 1, kvh = hq / gqa;
+                    const float* qv = q.data() + (size_t)t * qd + (size_t)hq * D;
+                    std::vector<float> s(n_keys);
+                    float mx = -INFINITY;
+                    for (int j = 0; j < n_keys; ++j) { s[j] = scale * dot(qv, kc.data() + (size_t)j * kvd + (size_t)kvh * D, D); mx = std::max(mx, s[j]); }
+                    float sum = 0;
+                    for (int j = 0; j < n_keys; ++j) { s[j] = std::exp(s[j] - mx); sum += s[j]; }
+                    float* o = att.data() + (size_t)t * qd + (size_t)hq * D;
+                    for (int d = 0; d < D; ++d) o[d] = 0;
+                    for (int j = 0; j < n_keys; ++j) { const float w = s[j] / sum; const float* vv = vc.data() + (size_t)j * kvd + (size_t)kvh * D; for (int d = 0; d < D; ++d) o[d] += w * vv[d]; }
+                }
+            matmul(g.get(p + "attn_output.weight"), att.data(), T, h.data(), true);
+            rmsnorm(h.data(), (const float*)g.get(p + "ffn_norm.weight").data, hp.eps, T, E, xn.data());
+            matmul(g.get(p + "ffn_gate.weight"), xn.data(), T, gate.data());
+            matmul(g.get(p + "ffn_up.weight"), xn.data(), T, up.data());
+            for (size_t i = 0; i < (size_t)T * F; ++i) gate[i] = gate[i] / (1.0f + std::exp(-gate[i])) * up[i];
+            matmul(g.get(p + "ffn_down.weight"), gate.data(), T, h.data(), true);
+        }
+        c.len = pos0 + T;
+        if (!last) return h;
+        const bool all = flags & 1u;
+        const int R = all ? T : 1;
+        const float* src = all ? h.data() : h.data() + (size_t)(T - 1) * E;
+        std::vector<float> hn((size_t)R * E), logits((size_t)R * hp.n_vocab);
+        rmsnorm(src, (const float*)g.get("output_norm.weight").data, hp.eps, R, E, hn.data());
+        matmul(g.has("output.weight") ? g.get("output.weight") : g.get("token_embd.weight"), hn.data(), R, logits.data());
+        return logits;
+    }
+};
+
+// ---- wire ----------------------------------------------------------------------------------------------------------------
+bool recv_all(int fd, void* p, size_t n) { uint8_t* b = (uint8_t*)p; while (n) { ssize_t r = ::recv(fd, b, n, 0); if (r <= 0) return false; b += r; n -= (size_t)r; } return true; }
+bool send_all(int fd, const void* p, size_t n) { const uint8_t* b = (const uint8_t*)p; while (n) { ssize_t r = ::send(fd, b, n, MSG_NOSIGNAL); if (r <= 0) return false; b += r; n -= (size_t)r; } return true; }
+bool reply(int fd, uint32_t status, const void* p, uint64_t n) { return send_all(fd, &status, 4) && send_all(fd, &n, 8) && (n == 0 || send_all(fd, p, n)); }
+
+#pragma pack(push, 1)
+struct ReqHeader { uint8_t cmd; uint32_t seq, n_tokens, pos0, flags; uint64_t nbytes; };
+struct Info { uint32_t version, n_embd, n_vocab, n_layer, l0, l1, first, last, n_ctx; };
+#pragma pack(pop)
+
+bool serve_client(int fd, Stage& st, bool verbose) {
+    std::vector<uint8_t> payload;
+    bool hello = false;
+    for (;;) {
+        ReqHeader rq;
+        if (!recv_all(fd, &rq, sizeof rq)) return true;
+        if (rq.nbytes > (uint64_t)st.hp.n_ctx * st.hp.n_embd * 4 + 64) { reply(fd, 2, "payload too large", 17); return true; }
+        payload.resize(rq.nbytes);
+        if (rq.nbytes && !recv_all(fd, payload.data(), rq.nbytes)) return true;
+        if (!hello && rq.cmd != HELLO) { reply(fd, 3, "HELLO first", 11); return true; }   // same rule as the reference (ggml-rpc.cpp:1584)
+        try {
+            switch (rq.cmd) {
+                case HELLO: {
+                    uint32_t ver = 0;
+                    if (rq.nbytes >= 4) memcpy(&ver, payload.data(), 4);
+                    if (ver != PROTO_VERSION) { reply(fd, 4, "protocol version mismatch", 25); return true; }
+                    hello = true;
+                    Info in{PROTO_VERSION, (uint32_t)st.hp.n_embd, (uint32_t)st.hp.n_vocab, (uint32_t)st.hp.n_layer, (uint32_t)st.l0, (uint32_t)st.l1,
+                            st.first, st.last, (uint32_t)st.hp.n_ctx};
+                    reply(fd, 0, &in, sizeof in);
+                    break;
+                }
+                case RUN: {
+                    std::vector<float> out = st.run(rq.seq, (int)rq.n_tokens, (int)rq.pos0, rq.flags, payload.data(), payload.size());
+                    if (verbose) fprintf(stderr, "RPC worker[%d:%d) seq %u: %u tokens @%u -> %zu floats\n", st.l0, st.l1, rq.seq, rq.n_tokens, rq.pos0, out.size());
+                    if (!reply(fd, 0, out.data(), out.size() * 4)) return true;
+                    break;
+                }
+                case RESET: st.seqs.erase(rq.seq); reply(fd, 0, nullptr, 0); break;
+                case TRUNCATE: { auto it = st.seqs.find(rq.seq); if (it != st.seqs.end()) it->second.len = std::min<int>(it->second.len, (int)rq.pos0); reply(fd, 0, nullptr, 0); break; }
+                case SHUTDOWN: reply(fd, 0, nullptr, 0); return false;
+                default: reply(fd, 5, "unknown command", 15); return true;
+            }
+        } catch (const std::exception& e) {
+            const std::string m = e.what();
+            if (!reply(fd, 1, m.data(), m.size())) return true;
+        }
+    }
+}
+
+}  // namespace
+
+int main(int argc, char** argv) {
+    signal(SIGPIPE, SIG_IGN);
+    std::string model, host = "127.0.0.1";
+    int port = 50052, l0 = 0, l1 = -1, n_ctx = 2048;
+    bool verbose = false;
+    for (int i = 1; i < argc; ++i) {
+        std::string a = argv[i];
+        auto next = [&]() -> std::string { if (i + 1 >= argc) { fprintf(stderr, "missing value for %s\n", a.c_str()); exit(2); } return argv[++i]; };
+        if (a == "-m" || a == "--model") model = next();
+        else if (a == "-H" || a == "--host") host = next();
+        else if (a == "-p" || a == "--port") port = atoi(next().c_str());
+        else if (a == "--layers") { std::string v = next(); size_t c = v.find(':'); l0 = atoi(v.substr(0, c).c_str()); l1 = c == std::string::npos ? -1 : atoi(v.substr(c + 1).c_str()); }
+        else if (a == "-c" || a == "--ctx-size") n_ctx = atoi(next().c_str());
+        else if (a == "-v" || a == "--verbose") verbose = true;
+        else { fprintf(stderr, "dlp-worker -m model.gguf [--layers a:b] [-H host] [-p port] [-c n_ctx] [-v]\n"); return a == "-h" ? 0 : 2; }
+    }
+    if (model.empty()) { fprintf(stderr, "dlp-worker: -m model.gguf is required\n"); return 2; }
+    Stage st;
+    try { st.load(model, l0, l1, n_ctx); } catch (const std::exception& e) { fprintf(stderr, "dlp-worker: %s\n", e.what()); return 1; }
+    if (host != "127.0.0.1" && host != "localhost")
+        fprintf(stderr, "WARNING: listening on %s - the worker protocol is unauthenticated; never expose it to an untrusted network\n", host.c_str());
+    int ls = ::socket(AF_INET, SOCK_STREAM, 0), one = 1;
+    setsockopt(ls, SOL_SOCKET, SO_REUSEADDR, &one, sizeof one);
+    sockaddr_in addr{};
+    addr.sin_family = AF_INET; addr.sin_port = htons((uint16_t)port);
+    if (inet_pton(AF_INET, host == "localhost" ? "127.0.0.1" : host.c_str(), &addr.sin_addr) != 1) addr.sin_addr.s_addr = htonl(INADDR_LOOPBACK);
+    if (bind(ls, (sockaddr*)&addr, sizeof addr) != 0 || listen(ls, 4) != 0) { perror("bind/listen"); return 1; }
+    fprintf(stderr, "RPC worker ready on %s:%d | layers [%d, %d) of %d%s%s | n_ctx %d\n", host.c_str(), port, st.l0, st.l1, st.hp.n_layer,
+            st.first ? " +embedding" : "", st.last ? " +lm_head" : "", n_ctx);
+    for (;;) {
+        int fd = ::accept(ls, nullptr, nullptr);
+        if (fd < 0) continue;
+        setsockopt(fd, IPPROTO_TCP, TCP_NODELAY, &one, sizeof one);
+        const bool keep = serve_client(fd, st, verbose);
+        ::close(fd);
+        st.seqs.clear();  // a client's buffers do not outlive its connection (as the reference frees per client)
+        if (!keep) break;
+    }
+    return 0;
+}

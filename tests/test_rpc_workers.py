@@ -1,0 +1,73 @@
+"""Config 1 path: two native CPU workers on localhost, each owning half of the layers, chained by the client.
+Oracle: the fp32 reference model on the same GGUF (what the reference's rpc-server pair + llama-cli would compute)."""
+import socket
+
+import pytest
+import torch
+
+from distributed_llm_pipeline_b200.models.reference import ReferenceModel, nmse
+from distributed_llm_pipeline_b200.parallel.rpc import RpcEngine, WorkerClient, WorkerError, launch_local_workers
+from distributed_llm_pipeline_b200.serving.sampler import SamplingParams
+from distributed_llm_pipeline_b200.serving.scheduler import Scheduler
+from distributed_llm_pipeline_b200.utils.tokenizer import Tokenizer
+
+
+def _free_ports(n):
+    socks = [socket.socket() for _ in range(n)]
+    for s in socks:
+        s.bind(("127.0.0.1", 0))
+    ports = [s.getsockname()[1] for s in socks]
+    for s in socks:
+        s.close()
+    return ports
+
+
+@pytest.fixture(scope="module", params=["Q8_0", "Q4_K_M"])
+def chain(request, tmp_models):
+    path = tmp_models[("tiny", request.param)]
+    base = _free_ports(1)[0]
+    procs, eps = launch_local_workers(path, 2, base_port=base, n_ctx=128, threads=2)
+    eng = RpcEngine(eps, max_seqs=2)
+    yield path, eng, eps
+    for w in eng.workers:
+        w.shutdown()
+    for p in procs:
+        p.wait(timeout=10)
+
+
+def test_two_worker_pipeline_matches_oracle(chain):
+    path, eng, _ = chain
+    ref = ReferenceModel.from_gguf(path)
+    prompt = [1, 5, 9, 200, 33, 7, 8, 100, 42]
+    toks, ref_logits = ref.generate_greedy(prompt, 4)
+    sid = eng.alloc_seq()
+    assert nmse(ref_logits[0], eng.prefill(sid, prompt)) < 1e-6
+    for i, t in enumerate(toks[:-1]):
+        assert nmse(ref_logits[i + 1], eng.decode([sid], [t], sample=False)[0]) < 1e-6
+    # truncate = prefix reuse: rewind to the prompt and replay one step
+    eng.truncate_seq(sid, len(prompt))
+    assert nmse(ref_logits[1], eng.decode([sid], [toks[0]], sample=False)[0]) < 1e-6
+    eng.free_seq(sid)
+    assert [w.l0 for w in eng.workers] == [0, 1] and eng.workers[0].first and eng.workers[1].last
+
+
+def test_scheduler_serves_through_workers(chain):
+    path, eng, _ = chain
+    sched = Scheduler(eng, Tokenizer.from_gguf(path), n_batch=32)
+    r = sched.generate("hello there", n_predict=5, sampling=SamplingParams(temperature=0.0))
+    assert 1 <= len(r.output_ids) <= 5 and r.finish_reason in ("length", "stop")
+    assert any("RPC worker" in l for l in eng.describe())
+
+
+def test_worker_validates_requests(chain):
+    _, eng, eps = chain
+    host, port = eps[0].split(":")
+    # the worker serves one client at a time (like the reference's rpc-server); reuse the engine's connection
+    w = eng.workers[0]
+    with pytest.raises(WorkerError, match="does not continue"):
+        w.run(7, 1, 5, b"\x01\x00\x00\x00")                 # position gap
+    with pytest.raises(WorkerError, match="payload size"):
+        w.run(7, 2, 0, b"\x01\x00\x00\x00")                 # 2 tokens announced, 1 sent
+    with pytest.raises(WorkerError, match="out of range"):
+        w.run(7, 1, 0, (10 ** 6).to_bytes(4, "little"))     # token id beyond the vocabulary
+    w.reset(7)
