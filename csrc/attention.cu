@@ -22,6 +22,7 @@ __global__ void __launch_bounds__(128) attn_decode_kernel(const AttnParams p) {
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int grp = lane >> 3, sub = lane & 7;
 
+    pdl_wait();
     const int len = p.kv_len[qi];
     const int per = (len + p.n_splits - 1) / p.n_splits;
     const int begin = split * per, end = min(len, begin + per);
@@ -89,6 +90,7 @@ __global__ void __launch_bounds__(128) attn_decode_kernel(const AttnParams p) {
             for (int i = 0; i < DL; ++i) o[g][i] = fmaf(pr, vf[i], o[g][i] * alpha);
         }
     }
+    pdl_launch_dependents();
     // merge the 4 lane groups of the warp, then the 4 warps of the CTA
     __shared__ float sm_m[4][G], sm_l[4][G];
     __shared__ float sm_o[4][G][D];
@@ -143,6 +145,8 @@ template <int D>
 __global__ void attn_combine_kernel(const AttnParams p) {
     const int hq = blockIdx.x, qi = blockIdx.y;
     const size_t pi0 = ((size_t)qi * p.Hq + hq) * p.n_splits;
+    pdl_wait();
+    pdl_launch_dependents();
     float mn = -INFINITY;
     for (int s = 0; s < p.n_splits; ++s) mn = fmaxf(mn, p.part_ml[(pi0 + s) * 2]);
     for (int d = threadIdx.x; d < D; d += blockDim.x) {
@@ -162,14 +166,10 @@ static int launch_attn(const AttnParams& p, cudaStream_t s) {
     const int gqa = p.Hq / p.Hkv;
     const int G = gqa % 4 == 0 ? 4 : (gqa % 2 == 0 ? 2 : 1);
     dim3 grid(p.n_splits, p.Hkv * (gqa / G), p.nq);
-    if (G == 4) attn_decode_kernel<D, 4><<<grid, 128, 0, s>>>(p);
-    else if (G == 2) attn_decode_kernel<D, 2><<<grid, 128, 0, s>>>(p);
-    else attn_decode_kernel<D, 1><<<grid, 128, 0, s>>>(p);
-    DLP_LAUNCH_CHECK();
-    if (p.n_splits > 1) {
-        attn_combine_kernel<D><<<dim3(p.Hq, p.nq), D, 0, s>>>(p);
-        DLP_LAUNCH_CHECK();
-    }
+    if (G == 4) DLP_CHECK_CUDA(launch_pdl(attn_decode_kernel<D, 4>, grid, dim3(128), 0, s, p));
+    else if (G == 2) DLP_CHECK_CUDA(launch_pdl(attn_decode_kernel<D, 2>, grid, dim3(128), 0, s, p));
+    else DLP_CHECK_CUDA(launch_pdl(attn_decode_kernel<D, 1>, grid, dim3(128), 0, s, p));
+    if (p.n_splits > 1) DLP_CHECK_CUDA(launch_pdl(attn_combine_kernel<D>, dim3(p.Hq, p.nq), dim3(D), 0, s, p));
     return 0;
 }
 

@@ -1,5 +1,6 @@
 // extern "C" surface of libdlp_b200.so (declarations: include/dlp_b200.h).
 #include <stdarg.h>
+#include <stdlib.h>
 #include <string.h>
 
 #include "../include/dlp_b200.h"
@@ -16,6 +17,16 @@ void set_error(const char* fmt, ...) {
     va_end(ap);
 }
 const char* get_error() { return g_err; }
+
+static int g_pdl = -1;
+bool pdl_enabled() {
+    if (g_pdl < 0) {
+        const char* e = getenv("DLP_PDL");
+        g_pdl = (e && e[0] == '0') ? 0 : 1;
+    }
+    return g_pdl != 0;
+}
+void set_pdl(bool on) { g_pdl = on ? 1 : 0; }
 
 int sm_count() {
     static int cached[64] = {0};
@@ -49,6 +60,7 @@ extern "C" {
 const char* dlp_last_error(void) { return get_error(); }
 int dlp_version(void) { return 100; }
 int dlp_sm_count(void) { return sm_count(); }
+int dlp_set_pdl(int on) { set_pdl(on != 0); return 0; }
 
 int dlp_gemv(const dlp_weight* w0, const dlp_weight* w1, const void* x, const float* norm_w, float eps, void* y,
              int ldy, int out_mode, int T, void* stream) {

@@ -6,13 +6,17 @@
 // rows straight into the peers' buffers over NVLink (gemv.cu, GV_PUSH_F32) and the next kernel's prologue
 // sums them (ArIn).  This file provides the allocation / handle exchange primitives, the epoch counter bump
 // and a stand-alone consumer for places where no mat-vec follows (pipeline-stage boundary).
+#include <string.h>
+
 #include "kernels.cuh"
 
 namespace dlp {
 
-__global__ void bump_kernel(int* ctr) { *ctr += 1; }
+__global__ void bump_kernel(int* ctr) { pdl_wait(); pdl_launch_dependents(); *ctr += 1; }
 
 __global__ void __launch_bounds__(256) ar_consume_kernel(const float* __restrict__ h_in, float* __restrict__ h_out, const ArIn a, int K, int T) {
+    pdl_wait();
+    pdl_launch_dependents();
     if ((int)threadIdx.x < a.tp) {
         const uint32_t want = (uint32_t)*a.epoch;
         const long long t0 = clock64();
@@ -36,14 +40,12 @@ __global__ void __launch_bounds__(256) ar_consume_kernel(const float* __restrict
 
 int ar_consume(const float* h_in, float* h_out, const ArIn& a, int K, int T, cudaStream_t s) {
     DLP_REQUIRE(a.buf && a.flags && a.epoch && a.tp >= 1 && a.tp <= 8, "ar_consume: bad descriptor");
-    ar_consume_kernel<<<T, 256, 0, s>>>(h_in, h_out, a, K, T);
-    DLP_LAUNCH_CHECK();
+    DLP_CHECK_CUDA(launch_pdl(ar_consume_kernel, dim3(T), dim3(256), 0, s, h_in, h_out, a, K, T));
     return 0;
 }
 
 int bump(int* ctr, cudaStream_t s) {
-    bump_kernel<<<1, 1, 0, s>>>(ctr);
-    DLP_LAUNCH_CHECK();
+    DLP_CHECK_CUDA(launch_pdl(bump_kernel, dim3(1), dim3(1), 0, s, ctr));
     return 0;
 }
 

@@ -45,6 +45,8 @@ const char* get_error();
     } while (0)
 
 int sm_count();  // cached multiprocessor count of the current device
+bool pdl_enabled();  // programmatic dependent launch between consecutive kernels (env DLP_PDL=0 disables)
+void set_pdl(bool on);
 
 // weight storage types understood by the kernels (values mirror GGML type ids where one exists)
 enum WType : int {
@@ -220,6 +222,31 @@ __device__ __forceinline__ bool elect_one() {
     return pred != 0;
 }
 
+// ---- programmatic dependent launch (PDL) ---------------------------------------------------------------
+// Every kernel of the decode chain calls pdl_wait() before it touches memory written by its predecessor and
+// pdl_launch_dependents() once its main loop is done, so the next kernel's launch latency, weight prefetch and
+// barrier/TMEM set-up overlap the tail of the current one.  Without the launch attribute both are no-ops.
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+__device__ __forceinline__ void prefetch_l2(const void* p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p)); }
+
 #endif  // __CUDACC__
+
+#ifdef __CUDACC__
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_pdl(void (*kern)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t stream, Args&&... args) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = grid;
+    cfg.blockDim = block;
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = pdl_enabled() ? 1 : 0;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    return cudaLaunchKernelEx(&cfg, kern, static_cast<KArgs>(args)...);
+}
+#endif
 
 }  // namespace dlp

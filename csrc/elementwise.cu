@@ -31,6 +31,8 @@ template <int WT, typename OutT>
 __global__ void dequant_rows_kernel(const QWeight w, const int* __restrict__ row_ids, OutT* __restrict__ out, int ld_out) {
     // grid.x = output rows; each thread decodes 32-element chunks
     const int orow = blockIdx.x;
+    pdl_wait();
+    pdl_launch_dependents();
     const int row = row_ids ? row_ids[orow] : orow;
     const int nchunk = w.K / 32;
     for (int c = threadIdx.x; c < nchunk; c += blockDim.x) {
@@ -49,6 +51,8 @@ __global__ void dequant_rows_kernel(const QWeight w, const int* __restrict__ row
 template <typename InT, typename OutT>
 __global__ void dense_rows_kernel(const InT* __restrict__ w, int K, const int* __restrict__ row_ids, OutT* __restrict__ out, int ld_out) {
     const int orow = blockIdx.x;
+    pdl_wait();
+    pdl_launch_dependents();
     const int row = row_ids ? row_ids[orow] : orow;
     for (int k = threadIdx.x; k < K; k += blockDim.x) out[(size_t)orow * ld_out + k] = (OutT)(float)w[(size_t)row * K + k];
 }
@@ -58,13 +62,13 @@ static int dequant_rows_t(const QWeight& w, int wtype, const int* row_ids, int n
     DLP_REQUIRE(n_rows > 0, "dequant_rows: no rows");
     const int threads = 128;
     switch (wtype) {
-        case W_F16: dense_rows_kernel<__half, OutT><<<n_rows, 256, 0, s>>>((const __half*)w.base, w.K, row_ids, out, ld_out); break;
-        case W_BF16: dense_rows_kernel<__nv_bfloat16, OutT><<<n_rows, 256, 0, s>>>((const __nv_bfloat16*)w.base, w.K, row_ids, out, ld_out); break;
-        case W_F32: dense_rows_kernel<float, OutT><<<n_rows, 256, 0, s>>>((const float*)w.base, w.K, row_ids, out, ld_out); break;
-        case W_Q8_0: dequant_rows_kernel<W_Q8_0, OutT><<<n_rows, threads, 0, s>>>(w, row_ids, out, ld_out); break;
-        case W_Q4_K: dequant_rows_kernel<W_Q4_K, OutT><<<n_rows, threads, 0, s>>>(w, row_ids, out, ld_out); break;
-        case W_Q5_K: dequant_rows_kernel<W_Q5_K, OutT><<<n_rows, threads, 0, s>>>(w, row_ids, out, ld_out); break;
-        case W_Q6_K: dequant_rows_kernel<W_Q6_K, OutT><<<n_rows, threads, 0, s>>>(w, row_ids, out, ld_out); break;
+        case W_F16: DLP_CHECK_CUDA(launch_pdl(dense_rows_kernel<__half, OutT>, dim3(n_rows), dim3(256), 0, s, (const __half*)w.base, w.K, row_ids, out, ld_out)); break;
+        case W_BF16: DLP_CHECK_CUDA(launch_pdl(dense_rows_kernel<__nv_bfloat16, OutT>, dim3(n_rows), dim3(256), 0, s, (const __nv_bfloat16*)w.base, w.K, row_ids, out, ld_out)); break;
+        case W_F32: DLP_CHECK_CUDA(launch_pdl(dense_rows_kernel<float, OutT>, dim3(n_rows), dim3(256), 0, s, (const float*)w.base, w.K, row_ids, out, ld_out)); break;
+        case W_Q8_0: DLP_CHECK_CUDA(launch_pdl(dequant_rows_kernel<W_Q8_0, OutT>, dim3(n_rows), dim3(threads), 0, s, w, row_ids, out, ld_out)); break;
+        case W_Q4_K: DLP_CHECK_CUDA(launch_pdl(dequant_rows_kernel<W_Q4_K, OutT>, dim3(n_rows), dim3(threads), 0, s, w, row_ids, out, ld_out)); break;
+        case W_Q5_K: DLP_CHECK_CUDA(launch_pdl(dequant_rows_kernel<W_Q5_K, OutT>, dim3(n_rows), dim3(threads), 0, s, w, row_ids, out, ld_out)); break;
+        case W_Q6_K: DLP_CHECK_CUDA(launch_pdl(dequant_rows_kernel<W_Q6_K, OutT>, dim3(n_rows), dim3(threads), 0, s, w, row_ids, out, ld_out)); break;
         default: DLP_REQUIRE(false, "dequant_rows: unsupported weight type %d", wtype);
     }
     DLP_LAUNCH_CHECK();
@@ -84,6 +88,8 @@ __global__ void __launch_bounds__(256) rmsnorm_kernel(float* __restrict__ h, con
                                                       const float* __restrict__ w, __half* __restrict__ out, int E, float eps) {
     __shared__ float red[32];
     const size_t base = (size_t)blockIdx.x * E;
+    pdl_wait();
+    pdl_launch_dependents();
     float ss = 0.f;
     for (int k = threadIdx.x * 4; k < E; k += blockDim.x * 4) {
         float4 v = *reinterpret_cast<const float4*>(h + base + k);
@@ -111,8 +117,7 @@ __global__ void __launch_bounds__(256) rmsnorm_kernel(float* __restrict__ h, con
 
 int rmsnorm(float* h, const float* delta, const float* w, __half* out, int T, int E, float eps, cudaStream_t s) {
     DLP_REQUIRE(E % 4 == 0 && T > 0, "rmsnorm: bad shape T=%d E=%d", T, E);
-    rmsnorm_kernel<<<T, 256, 0, s>>>(h, delta, w, out, E, eps);
-    DLP_LAUNCH_CHECK();
+    DLP_CHECK_CUDA(launch_pdl(rmsnorm_kernel, dim3(T), dim3(256), 0, s, h, delta, w, out, E, eps));
     return 0;
 }
 
@@ -127,6 +132,8 @@ __global__ void rope_kv_kernel(const InT* __restrict__ qkv, const int* __restric
                                __half* __restrict__ vc, int Hq, int Hkv, int D, int n_rot, int page_size, int neox, float q_scale) {
     const int t = blockIdx.x;
     const int H = Hq + 2 * Hkv;
+    pdl_wait();
+    pdl_launch_dependents();
     const float p = (float)pos[t];
     const int sl = slot[t];
     const int page = sl >= 0 ? sl / page_size : 0, off = sl >= 0 ? sl % page_size : 0;
@@ -167,10 +174,9 @@ int rope_kv(const void* qkv, int qkv_is_f16, const int* pos, const int* slot, co
             cudaStream_t s) {
     DLP_REQUIRE(T > 0 && D % 2 == 0 && n_rot <= D && n_rot % 2 == 0, "rope_kv: bad shape");
     if (qkv_is_f16)
-        rope_kv_kernel<__half><<<T, 256, 0, s>>>((const __half*)qkv, pos, slot, inv_freq, q_out, kc, vc, Hq, Hkv, D, n_rot, page_size, neox, q_scale);
+        DLP_CHECK_CUDA(launch_pdl(rope_kv_kernel<__half>, dim3(T), dim3(256), 0, s, (const __half*)qkv, pos, slot, inv_freq, q_out, kc, vc, Hq, Hkv, D, n_rot, page_size, neox, q_scale));
     else
-        rope_kv_kernel<float><<<T, 256, 0, s>>>((const float*)qkv, pos, slot, inv_freq, q_out, kc, vc, Hq, Hkv, D, n_rot, page_size, neox, q_scale);
-    DLP_LAUNCH_CHECK();
+        DLP_CHECK_CUDA(launch_pdl(rope_kv_kernel<float>, dim3(T), dim3(256), 0, s, (const float*)qkv, pos, slot, inv_freq, q_out, kc, vc, Hq, Hkv, D, n_rot, page_size, neox, q_scale));
     return 0;
 }
 
@@ -202,6 +208,8 @@ __global__ void advance_kernel(int* __restrict__ seq_len, const int* __restrict_
                                int* __restrict__ slot, int* __restrict__ kv_len, const int* __restrict__ block_table,
                                int max_pages, int page_size, int n) {
     const int s = blockIdx.x * blockDim.x + threadIdx.x;
+    pdl_wait();
+    pdl_launch_dependents();
     if (s >= n) return;
     const int sid = active ? active[s] : s;
     const int p = seq_len[sid];
@@ -213,8 +221,7 @@ __global__ void advance_kernel(int* __restrict__ seq_len, const int* __restrict_
 }
 int advance(int* seq_len, const int* active, int* pos, int* slot, int* kv_len, const int* block_table, int max_pages,
             int page_size, int n, cudaStream_t s) {
-    advance_kernel<<<(n + 127) / 128, 128, 0, s>>>(seq_len, active, pos, slot, kv_len, block_table, max_pages, page_size, n);
-    DLP_LAUNCH_CHECK();
+    DLP_CHECK_CUDA(launch_pdl(advance_kernel, dim3((n + 127) / 128), dim3(128), 0, s, seq_len, active, pos, slot, kv_len, block_table, max_pages, page_size, n));
     return 0;
 }
 
@@ -233,6 +240,8 @@ __global__ void __launch_bounds__(1024) argmax_kernel(const float* __restrict__ 
     __shared__ float sv[32];
     __shared__ int si[32];
     const float* row = logits + (size_t)blockIdx.x * ld;
+    pdl_wait();
+    pdl_launch_dependents();
     float best = -INFINITY;
     int bi = 0;
     for (int i = threadIdx.x; i < V; i += blockDim.x) {
@@ -264,8 +273,7 @@ __global__ void __launch_bounds__(1024) argmax_kernel(const float* __restrict__ 
 
 int argmax(const float* logits, int R, int V, int ld, int* out, cudaStream_t s) {
     DLP_REQUIRE(R > 0 && V > 0, "argmax: bad shape");
-    argmax_kernel<<<R, 1024, 0, s>>>(logits, V, ld, out);
-    DLP_LAUNCH_CHECK();
+    DLP_CHECK_CUDA(launch_pdl(argmax_kernel, dim3(R), dim3(1024), 0, s, logits, V, ld, out));
     return 0;
 }
 
@@ -281,6 +289,8 @@ __global__ void __launch_bounds__(1024) sample_kernel(const float* __restrict__ 
     __shared__ int ci[SAMPLE_MAX_CAND];
     __shared__ int s_n;
     const float* row = logits + (size_t)blockIdx.x * ld;
+    pdl_wait();
+    pdl_launch_dependents();
     const int k = max(1, min(top_k <= 0 ? SAMPLE_MAX_CAND : top_k, min(V, SAMPLE_MAX_CAND)));
     // bisection on the order-preserving integer image of the logits for the k-th largest value
     if (threadIdx.x == 0) { s_lo = 0u; s_hi = 0xffffffffu; }
@@ -362,8 +372,7 @@ int sample(const float* logits, int R, int V, int ld, int top_k, float top_p, fl
            const int* step_ctr, int* out, cudaStream_t s) {
     DLP_REQUIRE(R > 0 && V > 0, "sample: bad shape");
     if (temp <= 0.f) return argmax(logits, R, V, ld, out, s);
-    sample_kernel<<<R, 1024, 0, s>>>(logits, V, ld, top_k, top_p, min_p, temp, seed, step_ctr, out);
-    DLP_LAUNCH_CHECK();
+    DLP_CHECK_CUDA(launch_pdl(sample_kernel, dim3(R), dim3(1024), 0, s, logits, V, ld, top_k, top_p, min_p, temp, seed, step_ctr, out));
     return 0;
 }
 

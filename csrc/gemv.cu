@@ -142,13 +142,22 @@ __global__ void __launch_bounds__(256) gemv_dense_kernel(const GemvParams p) {
     const int K = p.w0.K, N = p.w0.N;
     __half* xs = reinterpret_cast<__half*>(gv_smem);
     __shared__ float red[32];
-    stage_x<NT>(p, K, xs, red);
-
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const bool dual = p.out_mode == GV_SWIGLU_F16;
     const int rows_per_it = dual ? 1 : 2;
     const int gw = blockIdx.x * 8 + warp, nw = gridDim.x * 8;
     constexpr int U = 4;
+    {   // weights do not depend on the previous kernel: pull this warp's first rows towards L2 while we wait for it
+        const int row = gw * rows_per_it;
+        if (row < N) {
+            const uint8_t* r0 = p.w0.base + (size_t)row * K * 2;
+            const uint8_t* r1 = dual ? p.w1.base + (size_t)row * K * 2 : p.w0.base + (size_t)min(row + 1, N - 1) * K * 2;
+            for (int b = lane * 128; b < K * 2; b += 32 * 128) { prefetch_l2(r0 + b); prefetch_l2(r1 + b); }
+        }
+    }
+    pdl_wait();
+    stage_x<NT>(p, K, xs, red);
+
     for (int row = gw * rows_per_it; row < N; row += nw * rows_per_it) {
         const uint8_t* wp[2];
         wp[0] = p.w0.base + (size_t)row * K * 2;
@@ -192,12 +201,14 @@ __global__ void __launch_bounds__(256) gemv_dense_kernel(const GemvParams p) {
                 }
             }
         }
+        if (row + nw * rows_per_it >= N) pdl_launch_dependents();  // last row group of this warp: let the next kernel ramp up
 #pragma unroll
         for (int s = 0; s < 2; ++s)
 #pragma unroll
             for (int t = 0; t < NT; ++t) acc[s][t] = warp_sum(acc[s][t]);
         gv_write<NT>(p, row, acc, dual, lane);
     }
+    pdl_launch_dependents();
     if (p.out_mode == GV_PUSH_F32) ar_signal(p.ar_out);
 }
 
@@ -210,6 +221,7 @@ __global__ void __launch_bounds__(256) gemv_quant_kernel(const GemvParams p) {
     // [NT][K/16] sums of x per 16 elements (placed after the optional fp32 AR staging row)
     float* xsum = reinterpret_cast<float*>(gv_smem + (size_t)NT * K * 2 + (p.ar_in.buf ? (size_t)K * 4 : 0));
     __shared__ float red[32];
+    pdl_wait();
     stage_x<NT>(p, K, xs, red);
     constexpr bool HAS_BIAS = (WT == W_Q4_K || WT == W_Q5_K);
     if (HAS_BIAS) {
@@ -272,6 +284,7 @@ __global__ void __launch_bounds__(256) gemv_quant_kernel(const GemvParams p) {
             for (int t = 0; t < NT; ++t) acc[s][t] = warp_sum(acc[s][t]);
         gv_write<NT>(p, row, acc, dual, lane);
     }
+    pdl_launch_dependents();
     if (p.out_mode == GV_PUSH_F32) ar_signal(p.ar_out);
 }
 
@@ -291,8 +304,7 @@ static int launch_gemv(Kern kern, const GemvParams& p, size_t smem, cudaStream_t
     int blocks = (p.w0.N + rows_per_block - 1) / rows_per_block;
     const int max_blocks = sm_count() * 4;
     if (blocks > max_blocks) blocks = max_blocks;
-    kern<<<blocks, 256, smem, stream>>>(p);
-    DLP_LAUNCH_CHECK();
+    DLP_CHECK_CUDA(launch_pdl(kern, dim3(blocks), dim3(256), smem, stream, p));
     return 0;
 }
 

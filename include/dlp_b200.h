@@ -41,6 +41,9 @@ enum { DLP_OUT_F16 = 0, DLP_OUT_F32 = 1, DLP_OUT_ADD_F32 = 2, DLP_OUT_SWIGLU_F16
 const char* dlp_last_error(void);
 int dlp_version(void);
 int dlp_sm_count(void);
+/* Programmatic dependent launch between consecutive kernels of a stream (default on; env DLP_PDL=0 or dlp_set_pdl(0)
+ * turns it off for A/B runs).  Kernels call griddepcontrol.wait before reading their predecessor's output. */
+int dlp_set_pdl(int on);
 
 /* Decode mat-vec, T in {1,2,4}: y[T,N] (op)= x[T,K] . W^T.  If norm_w != NULL, x is the fp32 residual stream and
  * RMSNorm(x)*norm_w is fused into the prologue; otherwise x is fp16.  out_mode SWIGLU takes w0=gate, w1=up.
