@@ -1,0 +1,89 @@
+"""Declarative flag table with environment fall-backs, shared by the tools.
+
+Parity: `common_params` + `common_arg{names, help, handler}.set_env("LLAMA_ARG_*")` (`llama.cpp/common/arg.cpp`,
+`common/common.h`): every option has CLI aliases and an env var; tools take subsets.  Flag names follow the reference
+where the concept exists (`-m -p -n -c -b -ub -np -ngl -sm -ts -mg --rpc -fa --temp --top-k --top-p --min-p --seed
+-v --log-file`); `-ngl` / `-fa` are accepted for command-line compatibility (all layers always live on the GPU and
+attention is always flash) and reported as such.
+"""
+from __future__ import annotations
+
+import argparse
+import os
+from dataclasses import dataclass
+
+
+@dataclass
+class Opt:
+    names: tuple
+    help: str
+    default: object = None
+    type: type | None = str
+    env: str | None = None
+    action: str | None = None
+    choices: tuple | None = None
+
+
+COMMON = [
+    Opt(("-m", "--model"), "GGUF checkpoint (first shard of a split set)", env="DLP_ARG_MODEL"),
+    Opt(("-c", "--ctx-size"), "context length per sequence", 2048, int, "DLP_ARG_CTX_SIZE"),
+    Opt(("-b", "--batch-size"), "max tokens per scheduling step (logical batch)", 2048, int, "DLP_ARG_BATCH"),
+    Opt(("-ub", "--ubatch-size"), "prefill chunk size (physical batch)", 512, int, "DLP_ARG_UBATCH"),
+    Opt(("-np", "--parallel"), "number of sequence slots", 1, int, "DLP_ARG_N_PARALLEL"),
+    Opt(("-ngl", "--gpu-layers", "--n-gpu-layers"), "accepted for compatibility: all layers are always GPU resident", 99, int, "DLP_ARG_N_GPU_LAYERS"),
+    Opt(("-sm", "--split-mode"), "none | layer (pipeline stages) | row (tensor parallel)", "layer", str, "DLP_ARG_SPLIT_MODE", choices=("none", "layer", "row")),
+    Opt(("-ts", "--tensor-split"), "comma separated stage weights for -sm layer (e.g. 3,1)", None, str, "DLP_ARG_TENSOR_SPLIT"),
+    Opt(("--pp",), "pipeline stages (explicit pp x tp grid; default from -sm)", None, int, "DLP_ARG_PP"),
+    Opt(("--tp",), "tensor-parallel ranks per stage", None, int, "DLP_ARG_TP"),
+    Opt(("--tp-impl",), "fused (in-kernel NVLink all-reduce) | nccl (baseline)", "fused", str, "DLP_TP_IMPL", choices=("fused", "nccl")),
+    Opt(("--rpc",), "comma separated host:port list of dlp-worker CPU stages", None, str, "DLP_ARG_RPC"),
+    Opt(("-fa", "--flash-attn"), "accepted for compatibility: attention is always flash", "on", str, "DLP_ARG_FLASH_ATTN"),
+    Opt(("--device",), "cuda | cpu", "cuda", str, "DLP_ARG_DEVICE"),
+    Opt(("-v", "--verbose"), "debug logging", False, None, "DLP_ARG_VERBOSE", action="store_true"),
+    Opt(("--log-file",), "also write logs to this file", None, str, "DLP_ARG_LOG_FILE"),
+    Opt(("--trace",), "write a chrome://tracing JSON of the run", None, str, "DLP_ARG_TRACE"),
+]
+SAMPLING = [
+    Opt(("--temp", "--temperature"), "sampling temperature (0 = greedy)", 0.8, float, "DLP_ARG_TEMP"),
+    Opt(("--top-k",), "top-k", 40, int, "DLP_ARG_TOP_K"),
+    Opt(("--top-p",), "top-p", 0.95, float, "DLP_ARG_TOP_P"),
+    Opt(("--min-p",), "min-p", 0.05, float, "DLP_ARG_MIN_P"),
+    Opt(("--typical",), "locally typical sampling p", 1.0, float, "DLP_ARG_TYPICAL"),
+    Opt(("--repeat-penalty",), "repetition penalty", 1.0, float, "DLP_ARG_REPEAT_PENALTY"),
+    Opt(("--presence-penalty",), "presence penalty", 0.0, float, "DLP_ARG_PRESENCE_PENALTY"),
+    Opt(("--frequency-penalty",), "frequency penalty", 0.0, float, "DLP_ARG_FREQUENCY_PENALTY"),
+    Opt(("-s", "--seed"), "RNG seed", 0, int, "DLP_ARG_SEED"),
+]
+GENERATION = [
+    Opt(("-p", "--prompt"), "prompt text", "", str, "DLP_ARG_PROMPT"),
+    Opt(("-f", "--file"), "read the prompt from a file", None, str),
+    Opt(("-n", "--predict", "--n-predict"), "tokens to generate", 200, int, "DLP_ARG_N_PREDICT"),
+    Opt(("--ignore-eos",), "keep generating after EOS", False, None, action="store_true"),
+    Opt(("-st", "--single-turn"), "exit after one reply", False, None, action="store_true"),
+]
+
+
+def build_parser(description: str, groups: list[list[Opt]]) -> argparse.ArgumentParser:
+    ap = argparse.ArgumentParser(description=description, formatter_class=argparse.ArgumentDefaultsHelpFormatter)
+    for g in groups:
+        for o in g:
+            default = o.default
+            if o.env and o.env in os.environ:
+                raw = os.environ[o.env]
+                default = (raw.lower() not in ("0", "false", "")) if o.action == "store_true" else (o.type(raw) if o.type else raw)
+            kw = dict(help=o.help + (f" [env {o.env}]" if o.env else ""), default=default)
+            if o.action:
+                kw["action"] = o.action
+            else:
+                kw["type"] = o.type
+                if o.choices:
+                    kw["choices"] = o.choices
+            ap.add_argument(*o.names, **kw)
+    return ap
+
+
+def sampling_from_args(a):
+    from ..serving.sampler import SamplingParams
+    return SamplingParams(temperature=a.temp, top_k=a.top_k, top_p=a.top_p, min_p=a.min_p, typical_p=a.typical,
+                          repeat_penalty=a.repeat_penalty, presence_penalty=a.presence_penalty,
+                          frequency_penalty=a.frequency_penalty, seed=a.seed)

@@ -1,0 +1,136 @@
+#!/usr/bin/env python
+"""dlp-bench: prompt-processing / text-generation throughput, llama-bench style.
+
+Parity: `llama-bench` (`llama.cpp/tools/llama-bench/llama-bench.cpp:1962-2010`): `-p` prompt sizes, `-n` generation sizes,
+`-r` repetitions, random token ids (valid with random-init weights), outputs md / json / csv with avg_ts +- stddev.
+Device-timed with CUDA events; under torchrun it runs the pp x tp grid and reports the max over ranks.
+"""
+import json
+import os
+import statistics
+import sys
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+
+import torch  # noqa: E402
+
+from distributed_llm_pipeline_b200.utils.args import COMMON, Opt, build_parser  # noqa: E402
+
+BENCH = [
+    Opt(("-p", "--n-prompt"), "comma separated prompt sizes", "512", str),
+    Opt(("-n", "--n-gen"), "comma separated generation sizes", "128", str),
+    Opt(("-r", "--repetitions"), "repetitions per test", 3, int),
+    Opt(("-o", "--output"), "md | json | csv", "md", str, choices=("md", "json", "csv")),
+    Opt(("--batch",), "decode batch size (sequences decoded together)", 1, int),
+]
+
+
+def main(argv=None):
+    a = build_parser("dlp-bench", [COMMON, BENCH]).parse_args(argv)
+    from distributed_llm_pipeline_b200.models.llama import LlamaEngine
+    from distributed_llm_pipeline_b200.models.weights import load_weights
+    from distributed_llm_pipeline_b200.parallel.grid import init_grid, stage_layer_ranges
+    from distributed_llm_pipeline_b200.utils.trace import max_over_ranks
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    pp = a.pp or (world if a.split_mode == "layer" and not a.tp else 1)
+    grid = init_grid(pp=pp, tp=a.tp, device=a.device)
+    comm = None
+    if grid.tp > 1:
+        if a.tp_impl == "fused":
+            from distributed_llm_pipeline_b200.parallel.fused import FusedComm
+            comm = FusedComm(grid)
+        else:
+            from distributed_llm_pipeline_b200.parallel.comm import NcclComm
+            comm = NcclComm(grid.tp_group, grid.tp, grid.tp_rank)
+    from distributed_llm_pipeline_b200.gguf import open_gguf
+    from distributed_llm_pipeline_b200.models.config import config_from_gguf
+    f = open_gguf(a.model)
+    cfg = config_from_gguf(f.metadata, f.tensors)
+    split = [float(x) for x in a.tensor_split.split(",")] if a.tensor_split else None
+    ranges = stage_layer_ranges(cfg.n_layer, grid.pp, split)
+    w = load_weights(f, grid.device, layer_range=ranges[grid.stage], tp_rank=grid.tp_rank, tp_size=grid.tp,
+                     first_stage=grid.first_stage, last_stage=grid.last_stage)
+    pps = [int(x) for x in a.n_prompt.split(",") if int(x) > 0]
+    gens = [int(x) for x in a.n_gen.split(",") if int(x) > 0]
+    n_ctx = max(pps + [0]) + max(gens + [0]) + 8
+    eng = LlamaEngine(w, n_ctx=max(n_ctx, a.ctx_size), max_seqs=max(1, a.batch), page_size=64, max_batch_tokens=max(a.ubatch_size, 16),
+                      comm=comm, first_stage=grid.first_stage, last_stage=grid.last_stage)
+    stage = None
+    if grid.pp > 1:
+        from distributed_llm_pipeline_b200.parallel.pp import PipelineStage
+        stage = PipelineStage(eng, grid)
+    cuda = grid.device.type == "cuda"
+    g = torch.Generator().manual_seed(0)
+    rows = []
+
+    def timed(fn):
+        if cuda:
+            torch.cuda.synchronize()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            fn()
+            e1.record()
+            torch.cuda.synchronize()
+            return max_over_ranks(e0.elapsed_time(e1), grid.device)
+        import time
+        t = time.perf_counter()
+        fn()
+        return max_over_ranks((time.perf_counter() - t) * 1e3, grid.device)
+
+    def fresh(n):
+        for s in list(eng.seqs):
+            eng.free_seq(s)
+        return [eng.alloc_seq() for _ in range(n)]
+
+    for n_p in pps:
+        ts = []
+        for rep in range(a.repetitions + 1):
+            sid = fresh(1)[0]
+            toks = torch.randint(3, cfg.vocab_size, (n_p,), generator=g, dtype=torch.int32)
+            ms = timed(lambda: (stage.prefill(sid, toks, chunk=a.ubatch_size) if stage else eng.prefill(sid, toks, chunk=a.ubatch_size)))
+            if rep:
+                ts.append(n_p / ms * 1e3)
+        rows.append({"test": f"pp{n_p}", "n_prompt": n_p, "n_gen": 0, "avg_ts": statistics.mean(ts), "stddev_ts": statistics.pstdev(ts)})
+    for n_g in gens:
+        ts = []
+        for rep in range(a.repetitions + 1):
+            sids = fresh(a.batch)
+            for s in sids:
+                (stage.prefill(s, [1]) if stage else eng.prefill(s, [1]))
+            first = torch.randint(3, cfg.vocab_size, (a.batch,), generator=g, dtype=torch.int32)
+
+            def run():
+                if stage:
+                    stage.decode_round([sids], [first])
+                    for _ in range(n_g - 1):
+                        stage.decode_round([sids], None)
+                else:
+                    eng.decode(sids, first)
+                    for _ in range(n_g - 1):
+                        eng.decode(sids)
+            ms = timed(run)
+            if rep:
+                ts.append(n_g * a.batch / ms * 1e3)
+        rows.append({"test": f"tg{n_g}" + (f"@b{a.batch}" if a.batch > 1 else ""), "n_prompt": 0, "n_gen": n_g, "avg_ts": statistics.mean(ts),
+                     "stddev_ts": statistics.pstdev(ts)})
+    if grid.rank == 0:
+        meta = {"model": os.path.basename(a.model), "params": cfg.n_params(), "size_bytes": w.nbytes(), "pp": grid.pp, "tp": grid.tp,
+                "tp_impl": a.tp_impl if grid.tp > 1 else None, "backend": "dlp_b200"}
+        if a.output == "json":
+            print(json.dumps([dict(meta, **r) for r in rows], indent=1))
+        elif a.output == "csv":
+            print("model,pp,tp,test,avg_ts,stddev_ts")
+            for r in rows:
+                print(f"{meta['model']},{grid.pp},{grid.tp},{r['test']},{r['avg_ts']:.2f},{r['stddev_ts']:.2f}")
+        else:
+            print("| model | size | pp x tp | test | t/s |\n|---|---:|---|---|---:|")
+            for r in rows:
+                print(f"| {meta['model']} | {w.nbytes() / 2**30:.2f} GiB/rank | {grid.pp} x {grid.tp} | {r['test']} | {r['avg_ts']:.2f} ± {r['stddev_ts']:.2f} |")
+    if grid.world > 1:
+        import torch.distributed as dist
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

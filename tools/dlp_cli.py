@@ -1,0 +1,76 @@
+#!/usr/bin/env python
+"""dlp-cli: single-process chat / completion front-end (the role `llama-cli` plays behind the reference orchestrator).
+
+Generated text goes to stdout (unbuffered), everything else to stderr - the split the reference orchestrator relies on
+(`orchestrator/src/main.rs:62-95`).  `--rpc a:p,b:p` runs the model on dlp-worker CPU stages, like the reference's
+`llama-cli --rpc 127.0.0.1:50052,127.0.0.1:50053` (`main.rs:47-48`).
+"""
+import os
+import sys
+import time
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+
+from distributed_llm_pipeline_b200.utils.args import COMMON, GENERATION, SAMPLING, build_parser, sampling_from_args  # noqa: E402
+from distributed_llm_pipeline_b200.utils.log import get_logger  # noqa: E402
+
+
+def main(argv=None):
+    a = build_parser("dlp-cli - generate text from a GGUF model", [COMMON, SAMPLING, GENERATION]).parse_args(argv)
+    if not a.model:
+        sys.exit("dlp-cli: -m model.gguf is required")
+    log = get_logger()
+    log.verbosity = 4 if a.verbose else 3
+    if a.log_file:
+        log.add_file(a.log_file)
+    import torch
+
+    from distributed_llm_pipeline_b200.serving.scheduler import Request, Scheduler
+    from distributed_llm_pipeline_b200.utils.tokenizer import Tokenizer
+    t0 = time.time()
+    if a.rpc:
+        from distributed_llm_pipeline_b200.parallel.rpc import RpcEngine
+        eng = RpcEngine(a.rpc.split(","), n_ctx=a.ctx_size, max_seqs=a.parallel)
+        for line in eng.describe():
+            log.info(line)
+        tok = Tokenizer.from_gguf(a.model)
+    else:
+        from distributed_llm_pipeline_b200.gguf import open_gguf
+        from distributed_llm_pipeline_b200.models.llama import LlamaEngine
+        from distributed_llm_pipeline_b200.models.weights import load_weights
+        dev = a.device if (a.device != "cuda" or torch.cuda.is_available()) else "cpu"
+        f = open_gguf(a.model)
+        w = load_weights(f, dev)
+        eng = LlamaEngine(w, n_ctx=a.ctx_size, max_seqs=a.parallel, page_size=64 if dev != "cpu" else 16,
+                          max_batch_tokens=min(a.batch_size, a.ubatch_size))
+        tok = Tokenizer(f.metadata)
+        log.info(f"load_tensors: offloaded {w.cfg.n_layer + 1}/{w.cfg.n_layer + 1} layers to GPU ({dev}), {w.nbytes() / 2**20:.1f} MiB")
+    log.info(f"model loaded in {time.time() - t0:.2f} s | n_ctx {a.ctx_size} | slots {a.parallel}")
+    sched = Scheduler(eng, tok, n_batch=a.batch_size)
+    prompt = open(a.file).read() if a.file else a.prompt
+
+    def on_event(kind, content):
+        if kind == "token":
+            sys.stdout.write(content)
+            sys.stdout.flush()
+        elif kind in ("log", "error"):
+            log.info(content.rstrip("\n"))
+
+    while True:
+        req = sched.generate(prompt, n_predict=a.predict, sampling=sampling_from_args(a), ignore_eos=a.ignore_eos, on_event=on_event)
+        sys.stdout.write("\n")
+        t = req.timings()
+        log.info(f"prompt eval: {t['prompt_n']} tokens, {t['prompt_per_second']} tok/s | eval: {t['predicted_n']} tokens, {t['predicted_per_second']} tok/s")
+        if a.single_turn or not sys.stdin.isatty():
+            break
+        try:
+            prompt = input("> ")
+        except EOFError:
+            break
+        if prompt.strip() in ("/exit", "/quit"):
+            break
+    log.flush()
+
+
+if __name__ == "__main__":
+    main()
