@@ -124,7 +124,16 @@ int dlp_linear(const dlp_weight* w0, const dlp_weight* w1, const void* x, const 
     if (wt == DLP_W_F16 || wt == DLP_W_BF16)
         return gemm_f16(w0->base, w1 ? w1->base : nullptr, w0->K, x, w0->K, y, ldy, T, w0->N, w0->K, epi,
                         wt == DLP_W_BF16, 0, s);
-    // block-quantised: decode to fp16 scratch, then the dense tensor-core GEMM
+    // block-quantised: the decode is fused into the GEMM's A-operand producer (no scratch).  DLP_GEMM_DEQUANT_SCRATCH=1
+    // selects the older two-pass path (decode to fp16 scratch, then the dense GEMM) for A/B runs.
+    static int two_pass = -1;
+    if (two_pass < 0) { const char* e = getenv("DLP_GEMM_DEQUANT_SCRATCH"); two_pass = (e && e[0] == '1') ? 1 : 0; }
+    if (!two_pass) {
+        const QWeight q0 = to_qw(w0);
+        QWeight q1;
+        if (w1) q1 = to_qw(w1);
+        return gemm_quant(q0, w1 ? &q1 : nullptr, wt, x, w0->K, y, ldy, T, epi, 0, s);
+    }
     const size_t per = (size_t)w0->N * w0->K * 2;
     const size_t need = per * (w1 ? 2 : 1);
     DLP_REQUIRE(scratch != nullptr && scratch_bytes >= need, "dlp_linear: scratch too small (%zu < %zu bytes)", scratch_bytes, need);

@@ -42,10 +42,64 @@ struct GemmCfg {
 
 __device__ __forceinline__ float silu_f(float x) { return x / (1.f + __expf(-x)); }
 
-template <int BT, int NA, int AB_FMT>
+// ---- dequant-fused A operand ---------------------------------------------------------------------------
+// For block-quantised weights the four epilogue warps (idle while the accumulator is being built) act as the
+// A-operand producer: thread r owns row r of the 128-row tile, decodes that row's 64-element K slice from
+// the GGUF blocks straight into shared memory as fp16 - in exactly the layout TMA would have produced
+// (128-byte rows, 16-byte chunks XOR-swizzled by row % 8) - then fences the generic-proxy writes towards the
+// async proxy and arrives on the stage's "full" barrier.  The tensor core never sees the difference; no
+// dequantised copy of the weights ever exists in global memory.
+template <int WT>
+__device__ __forceinline__ void dequant_row_slice(const QWeight& w, int row, int kc, uint8_t* tile, int r) {
+    uint8_t* dst = tile + r * 128;
+    const int sw = r & 7;
+    if (row >= w.N) {
+#pragma unroll
+        for (int c = 0; c < 8; ++c) *reinterpret_cast<uint4*>(dst + c * 16) = make_uint4(0, 0, 0, 0);
+        return;
+    }
+    constexpr int NCH = (WT == W_Q6_K) ? 4 : 2;
+    int cbase;
+    if (WT == W_Q8_0) cbase = kc >> 5;
+    else if (WT == W_Q6_K) cbase = (kc >> 8) * 8 + ((kc & 255) >> 7) * 4;
+    else cbase = (kc >> 8) * 8 + ((kc & 255) >> 6) * 2;
+    QChunk ch[NCH];
+#pragma unroll
+    for (int i = 0; i < NCH; ++i) load_chunk<WT>(w, row, cbase + i, ch[i]);   // all loads in flight before any math
+#pragma unroll
+    for (int i = 0; i < NCH; ++i) {
+#pragma unroll
+        for (int g = 0; g < 2; ++g) {
+            const int e0 = ch[i].k[g] - kc;   // 16-aligned element offset inside the 64-wide slice (or outside it)
+            if (e0 < 0 || e0 >= 64) continue;
+            uint32_t o[8];
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+                const float2 f = __half22float2(ch[i].q[g][j]);
+                const __half2 h = __floats2half2_rn(fmaf(ch[i].scale[g], f.x, ch[i].bias[g]), fmaf(ch[i].scale[g], f.y, ch[i].bias[g]));
+                o[j] = *reinterpret_cast<const uint32_t*>(&h);
+            }
+            const int c0 = e0 >> 3;
+            *reinterpret_cast<uint4*>(dst + ((c0 ^ sw) << 4)) = make_uint4(o[0], o[1], o[2], o[3]);
+            *reinterpret_cast<uint4*>(dst + (((c0 + 1) ^ sw) << 4)) = make_uint4(o[4], o[5], o[6], o[7]);
+        }
+    }
+}
+
+template <int WT>
+__device__ __forceinline__ void prefetch_row_slice(const QWeight& w, int row, int kc) {
+    if (row >= w.N || kc >= w.K) return;
+    if (WT == W_Q8_0) prefetch_l2(w.base + (size_t)row * w.K + kc);
+    else if (WT == W_Q4_K) prefetch_l2(w.base + ((size_t)row * (w.K >> 8) + (kc >> 8)) * 144 + 16 + ((kc & 255) >> 6) * 32);
+    else if (WT == W_Q5_K) prefetch_l2(w.base + ((size_t)row * (w.K >> 8) + (kc >> 8)) * 176 + 48 + ((kc & 255) >> 6) * 32);
+    else if (WT == W_Q6_K) prefetch_l2(w.base + ((size_t)row * (w.K >> 8) + (kc >> 8)) * 128 + ((kc & 255) >> 7) * 64);
+}
+
+template <int BT, int NA, int AB_FMT, int WT>
 __global__ void __launch_bounds__(192, 1)
 gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tm_w0, const __grid_constant__ CUtensorMap tm_w1,
-                    const __grid_constant__ CUtensorMap tm_x, const GemmParams p) {
+                    const __grid_constant__ CUtensorMap tm_x, const GemmParams p, const QWeight qw0, const QWeight qw1) {
+    constexpr bool QUANT = (WT != W_F16);
     using Cfg = GemmCfg<BT, NA>;
     constexpr int STAGES = Cfg::STAGES;
     extern __shared__ uint8_t smem_raw[];
@@ -74,7 +128,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tm_w0, const __grid_cons
         if (NA == 2) tma_prefetch_desc(&tm_w1);
         tma_prefetch_desc(&tm_x);
         for (int s = 0; s < STAGES; ++s) {
-            mbar_init(&full_bar[s], 1);
+            mbar_init(&full_bar[s], QUANT ? 5 : 1);   // TMA thread (+ one lane of each of the 4 dequant warps)
             mbar_init(&empty_bar[s], 1);
         }
         mbar_init(tmem_full_bar, 1);
@@ -96,10 +150,12 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tm_w0, const __grid_cons
             uint32_t phase = 0;
             for (int kb = 0; kb < num_kb; ++kb) {
                 mbar_wait(&empty_bar[stage], phase ^ 1);
-                mbar_expect_tx(&full_bar[stage], Cfg::STAGE_BYTES);
+                mbar_expect_tx(&full_bar[stage], QUANT ? Cfg::B_BYTES : Cfg::STAGE_BYTES);
                 const int kc = (kb_begin + kb) * GEMM_BK;
-                tma_load_2d(smem_a0 + stage * Cfg::A_BYTES, &tm_w0, &full_bar[stage], kc, n0);
-                if (NA == 2) tma_load_2d(smem_a1 + stage * Cfg::A_BYTES, &tm_w1, &full_bar[stage], kc, n0);
+                if (!QUANT) {
+                    tma_load_2d(smem_a0 + stage * Cfg::A_BYTES, &tm_w0, &full_bar[stage], kc, n0);
+                    if (NA == 2) tma_load_2d(smem_a1 + stage * Cfg::A_BYTES, &tm_w1, &full_bar[stage], kc, n0);
+                }
                 tma_load_2d(smem_b + stage * Cfg::B_BYTES, &tm_x, &full_bar[stage], kc, t0);
                 if (++stage == STAGES) { stage = 0; phase ^= 1; }
             }
@@ -129,6 +185,24 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tm_w0, const __grid_cons
             tc_commit(tmem_full_bar);  // accumulator complete
         }
     } else {
+        if constexpr (QUANT) {
+            // ===== dequant producers (the epilogue warps, before there is anything to drain) =====
+            const int r = (warp - 2) * 32 + lane;
+            int stage = 0;
+            uint32_t phase = 0;
+            for (int kb = 0; kb < num_kb; ++kb) {
+                const int kc = (kb_begin + kb) * GEMM_BK;
+                prefetch_row_slice<WT>(qw0, n0 + r, kc + 4 * GEMM_BK);
+                if (NA == 2) prefetch_row_slice<WT>(qw1, n0 + r, kc + 4 * GEMM_BK);
+                mbar_wait(&empty_bar[stage], phase ^ 1);
+                dequant_row_slice<WT>(qw0, n0 + r, kc, smem_a0 + stage * Cfg::A_BYTES, r);
+                if (NA == 2) dequant_row_slice<WT>(qw1, n0 + r, kc, smem_a1 + stage * Cfg::A_BYTES, r);
+                fence_proxy_async();   // generic-proxy smem writes -> visible to tcgen05 (async proxy)
+                __syncwarp();
+                if (lane == 0) mbar_arrive(&full_bar[stage]);
+                if (++stage == STAGES) { stage = 0; phase ^= 1; }
+            }
+        }
         // ===== epilogue: 4 warps, warp%4 selects the TMEM lane quarter =====
         const int q = warp & 3;
         const int n = n0 + q * 32 + lane;
@@ -221,18 +295,18 @@ int make_tmap_2d(CUtensorMap* out, const void* base, int is_bf16, uint64_t rows,
     return 0;
 }
 
-template <int BT, int NA, int AB_FMT>
+template <int BT, int NA, int AB_FMT, int WT = W_F16>
 static int launch_gemm(const CUtensorMap& tw0, const CUtensorMap& tw1, const CUtensorMap& tx, const GemmParams& p,
-                       int splits, cudaStream_t stream) {
+                       int splits, cudaStream_t stream, const QWeight& qw0 = QWeight(), const QWeight& qw1 = QWeight()) {
     using Cfg = GemmCfg<BT, NA>;
-    auto kern = gemm_tcgen05_kernel<BT, NA, AB_FMT>;
+    auto kern = gemm_tcgen05_kernel<BT, NA, AB_FMT, WT>;
     static bool configured = false;
     if (!configured) {
         DLP_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES));
         configured = true;
     }
     dim3 grid((p.N + GEMM_BM - 1) / GEMM_BM, (p.T + BT - 1) / BT, splits);
-    kern<<<grid, 192, Cfg::SMEM_BYTES, stream>>>(tw0, tw1, tx, p);
+    kern<<<grid, 192, Cfg::SMEM_BYTES, stream>>>(tw0, tw1, tx, p, qw0, qw1);
     DLP_LAUNCH_CHECK();
     return 0;
 }
@@ -285,6 +359,54 @@ int gemm_f16(const void* w0, const void* w1, int ldw, const void* x, int ldx, vo
     }
 #undef DLP_GEMM_CASE
     return -1;
+}
+
+// Y[T,N] (op)= X[T,K] . dequant(W)[N,K]^T with the block-quant decode fused into the A-operand producer.
+int gemm_quant(const QWeight& w0, const QWeight* w1, int wtype, const void* x, int ldx, void* y, int ldy, int T, int epilogue,
+               int split_k, cudaStream_t stream) {
+    const int N = w0.N, K = w0.K;
+    DLP_REQUIRE(T > 0 && N > 0 && K > 0 && K % 256 == 0, "gemm_quant: bad problem T=%d N=%d K=%d", T, N, K);
+    const int na = (epilogue == EPI_SWIGLU_F16) ? 2 : 1;
+    DLP_REQUIRE(na == 1 || w1 != nullptr, "gemm_quant: SwiGLU epilogue needs the up-projection weight");
+    const int total_kb = K / GEMM_BK;
+    int splits = split_k;
+    if (splits <= 0) {
+        splits = 1;
+        if (epilogue == EPI_ATOMIC_ADD_F32) {
+            const int bt_guess = T <= 16 ? 16 : T <= 32 ? 32 : T <= 64 ? 64 : T <= 128 ? 128 : 256;
+            const long tiles = (long)((N + GEMM_BM - 1) / GEMM_BM) * ((T + bt_guess - 1) / bt_guess);
+            const int sms = sm_count();
+            while (tiles * splits * 2 <= sms && total_kb / (splits * 2) >= 8) splits *= 2;
+        }
+    }
+    DLP_REQUIRE(splits == 1 || epilogue == EPI_ATOMIC_ADD_F32, "gemm_quant: split-K needs the atomic-add epilogue");
+    if (splits > total_kb) splits = total_kb;
+    GemmParams p;
+    p.y = y; p.T = T; p.N = N; p.K = K; p.ldy = ldy; p.epilogue = epilogue;
+    p.k_blocks_per_split = (total_kb + splits - 1) / splits;
+    splits = (total_kb + p.k_blocks_per_split - 1) / p.k_blocks_per_split;
+    const int bt = T <= 16 ? 16 : T <= 32 ? 32 : T <= 64 ? 64 : T <= 128 ? 128 : 256;
+    CUtensorMap tx;
+    int rc;
+    if ((rc = make_tmap_2d(&tx, x, 0, T, K, ldx, bt))) return rc;
+    const QWeight up = w1 ? *w1 : QWeight();
+#define DLP_QG_BT(WT_, BT_)                                                                                   \
+    case BT_:                                                                                                 \
+        return na == 2 ? launch_gemm<BT_, 2, 0, WT_>(tx, tx, tx, p, splits, stream, w0, up)                   \
+                       : launch_gemm<BT_, 1, 0, WT_>(tx, tx, tx, p, splits, stream, w0, up);
+#define DLP_QG_TYPE(WT_)                                                                                      \
+    case WT_:                                                                                                 \
+        switch (bt) { DLP_QG_BT(WT_, 16) DLP_QG_BT(WT_, 32) DLP_QG_BT(WT_, 64) DLP_QG_BT(WT_, 128) DLP_QG_BT(WT_, 256) } \
+        break;
+    switch (wtype) {
+        DLP_QG_TYPE(W_Q8_0)
+        DLP_QG_TYPE(W_Q4_K)
+        DLP_QG_TYPE(W_Q5_K)
+        DLP_QG_TYPE(W_Q6_K)
+    }
+#undef DLP_QG_TYPE
+#undef DLP_QG_BT
+    DLP_REQUIRE(false, "gemm_quant: unsupported weight type %d", wtype);
 }
 
 }  // namespace dlp

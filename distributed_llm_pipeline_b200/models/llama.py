@@ -170,6 +170,8 @@ class LlamaEngine:
         self.seq_len_dev[sid] = new_len
 
     def _scratch_for(self, *ws):
+        if not ops.TWO_PASS_DEQUANT:   # block-quant decode is fused into the GEMM: no scratch
+            return None
         need = 0
         for w in ws:
             if w is not None and w.dense is None and w.wtype.name.startswith("Q"):

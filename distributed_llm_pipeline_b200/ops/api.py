@@ -16,6 +16,9 @@ from .weights import DeviceWeight
 OUT_F16, OUT_F32, OUT_ADD_F32, OUT_SWIGLU_F16 = 0, 1, 2, 3
 _OUT = {"f16": OUT_F16, "f32": OUT_F32, "add": OUT_ADD_F32, "swiglu": OUT_SWIGLU_F16}
 
+import os as _os
+TWO_PASS_DEQUANT = _os.environ.get("DLP_GEMM_DEQUANT_SCRATCH", "0") == "1"
+
 # launch counter: every native kernel launch issued through this module (bench.py reports it)
 launch_count = 0
 
@@ -119,7 +122,7 @@ def linear(w: DeviceWeight, x: torch.Tensor, out_mode: str = "f16", w_up: Device
     elif x.dtype != torch.float16:
         x = x.to(torch.float16)
     quant = w.wtype.name.startswith("Q")
-    if quant:
+    if quant and TWO_PASS_DEQUANT:   # A/B path: decode to an fp16 scratch, then the dense GEMM (default: fused in-kernel)
         need = w.N * w.K * 2 * (2 if w_up is not None else 1)
         if scratch is None or scratch.numel() * scratch.element_size() < need:
             scratch = torch.empty(need, dtype=torch.uint8, device=x.device)

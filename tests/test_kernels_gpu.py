@@ -93,14 +93,35 @@ def test_gemm_tcgen05_ragged_n_splitk_swiglu():
     assert nmse(torch.nn.functional.silu(ref) * (x.float() @ u.float().T), sw) < 5e-6
 
 
-@pytest.mark.parametrize("t", [GGMLType.Q8_0, GGMLType.Q4_K, GGMLType.Q6_K])
-def test_linear_quant_gemm_path_uses_scratch(t):
-    T, N, K = 48, 256, 512
+@pytest.mark.parametrize("t", [GGMLType.Q8_0, GGMLType.Q4_K, GGMLType.Q5_K, GGMLType.Q6_K])
+@pytest.mark.parametrize("T,N,K", [(48, 256, 512), (300, 200, 1024), (7, 384, 2048)])
+def test_linear_quant_dequant_fused_gemm(t, T, N, K):
+    """Block-quant decode fused into the tcgen05 GEMM's A-operand producer (no scratch), all epilogues."""
     w, exact = _w(N, K, t, 4)
+    u, exact_u = _w(N, K, t, 5)
     x = torch.randn(T, K, device=DEV).half()
+    ref = x.float() @ exact.T
+    assert nmse(ref, ops.linear(w, x, "f32")) < 5e-6            # weights are rounded to fp16 after decode
+    assert nmse(ref, ops.linear(w, x, "f16")) < 5e-6
+    acc = torch.ones(T, N, device=DEV)
+    ops.linear(w, x, "add", out=acc)
+    assert nmse(ref + 1, acc) < 5e-6
+    sw = ops.linear(w, x, "swiglu", w_up=u)
+    assert nmse(torch.nn.functional.silu(ref) * (x.float() @ exact_u.T), sw) < 2e-5
+
+
+def test_linear_quant_two_pass_scratch_entry_point():
+    """dlp_linear's caller-provided-scratch contract still holds (used when DLP_GEMM_DEQUANT_SCRATCH=1)."""
+    import ctypes as C
+    from distributed_llm_pipeline_b200.ops import lib as L
+    T, N, K = 48, 256, 512
+    w, exact = _w(N, K, GGMLType.Q8_0, 4)
+    x = torch.randn(T, K, device=DEV).half()
+    y = torch.empty(T, N, device=DEV)
     scratch = torch.empty(N * K * 2, dtype=torch.uint8, device=DEV)
-    y = ops.linear(w, x, "f32", scratch=scratch)
-    assert nmse(x.float() @ exact.T, y) < 5e-6   # fp16-rounded dequant
+    rc = L.load().dlp_linear(w.ref(), None, x.data_ptr(), None, 0.0, y.data_ptr(), N, 1, T, scratch.data_ptr(), scratch.numel(),
+                             torch.cuda.current_stream().cuda_stream)
+    assert rc == 0 and nmse(x.float() @ exact.T, y) < 5e-6
 
 
 def test_rmsnorm_with_residual():
