@@ -1,0 +1,35 @@
+#!/usr/bin/env python
+"""Short deterministic workload for ncu: one pp<N> prefill + a few eager decode steps of the bench model."""
+import argparse
+import os
+import sys
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import torch  # noqa: E402
+
+from bench import ensure_model  # noqa: E402
+from distributed_llm_pipeline_b200.models.llama import LlamaEngine  # noqa: E402
+from distributed_llm_pipeline_b200.models.weights import load_weights  # noqa: E402
+
+ap = argparse.ArgumentParser()
+ap.add_argument("--model", default="llama-3-8b")
+ap.add_argument("--ftype", default="F16")
+ap.add_argument("--prefill", type=int, default=512)
+ap.add_argument("--decode", type=int, default=3)
+ap.add_argument("--layers", type=int, default=0, help="profile only the first N layers (0 = all)")
+a = ap.parse_args()
+path = ensure_model(a.model, a.ftype, 0, lambda: None)
+rng = range(a.layers) if a.layers else None
+w = load_weights(path, "cuda:0", layer_range=rng)
+eng = LlamaEngine(w, n_ctx=2048, max_seqs=1, page_size=64, max_batch_tokens=max(a.prefill, 16))
+sid = eng.alloc_seq()
+g = torch.Generator().manual_seed(0)
+if a.prefill:
+    eng.prefill(sid, torch.randint(3, eng.cfg.vocab_size, (a.prefill,), generator=g, dtype=torch.int32))
+else:
+    eng.prefill(sid, [1])
+torch.cuda.synchronize()
+for _ in range(a.decode):
+    eng.decode([sid], [5], use_graph=False)
+torch.cuda.synchronize()
+print("prof_step done")
