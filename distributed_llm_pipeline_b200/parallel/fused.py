@@ -100,6 +100,33 @@ class FusedComm(NcclComm):
         dist.barrier(group=self.group)
         self.ready = True
 
+    @classmethod
+    def make_virtual(cls, tp: int, n_embd: int, n_sites: int, device="cuda") -> list["FusedComm"]:
+        """`tp` communicators that live on ONE device and point at each other's buffers directly - no IPC, no process
+        group.  Used to test the push / flag / consume protocol on a single GPU: the caller launches each phase for all
+        virtual ranks in turn, so every flag is already published when a consumer looks at it (kernels that wait on each
+        other must never be co-scheduled on one GPU)."""
+        comms = []
+        for r in range(tp):
+            c = cls.__new__(cls)
+            c.group, c.tp_size, c.tp_rank, c._gather_buf = None, tp, r, None
+            c.grid, c.device, c.lib = None, torch.device(device), _lib.load()
+            c._declare()
+            c.E, c.n_sites = n_embd, n_sites
+            c.buf_bytes = tp * MAX_T * n_embd * 4
+            c.site_stride = c.buf_bytes + 256
+            c._mem = torch.zeros(n_sites * c.site_stride, dtype=torch.uint8, device=device)
+            c.base = c._mem.data_ptr()
+            c.epoch = torch.zeros(1, dtype=torch.int32, device=device)
+            c.done = torch.zeros(1, dtype=torch.int32, device=device)
+            c.error = torch.zeros(1, dtype=torch.int32, device=device)
+            c._in, c._out = {}, {}
+            c.ready = True
+            comms.append(c)
+        for c in comms:
+            c.peers = [o.base for o in comms]
+        return comms
+
     def ar_in(self, site: int, h_out: torch.Tensor) -> dlp_ar_in:
         key = (site, h_out.data_ptr())
         d = self._in.get(key)

@@ -228,3 +228,42 @@ def test_advance_bookkeeping():
     assert kvl.tolist() == [1, 16, 17]
     assert pos.tolist() == [0, 15, 16] and sl.tolist() == [1, 16, 17]
     assert slot.tolist() == [0 * 16 + 0, 4 * 16 + 15, 9 * 16 + 0]
+
+
+@pytest.mark.parametrize("t", [GGMLType.F16, GGMLType.Q8_0, GGMLType.Q4_K])
+@pytest.mark.parametrize("T", [1, 2, 4])
+def test_fused_allreduce_protocol_virtual_ranks(t, T):
+    """Row-parallel GEMV -> push to every peer's reduce buffer + flag; next GEMV's prologue folds h += sum(partials)
+    into its RMSNorm.  Four virtual ranks on one GPU, phases launched rank by rank (no co-scheduled waiting kernels)."""
+    from distributed_llm_pipeline_b200.parallel.fused import FusedComm
+    tp, E, F = 4, 512, 1024
+    comms = FusedComm.make_virtual(tp, E, n_sites=2)
+    g = torch.Generator().manual_seed(11)
+    w_down = torch.randn(E, F, generator=g) * 0.05          # row-parallel: K = F sharded
+    w_next = torch.randn(256, E, generator=g) * 0.05         # next column-parallel matrix (replicated here)
+    nw = (torch.rand(E, generator=g) + 0.5).to(DEV)
+    act = (torch.randn(T, F, generator=g)).half().to(DEV)
+    h = torch.randn(T, E, generator=g).to(DEV)
+    Fs = F // tp
+    shards = [DeviceWeight.from_dense(w_down[:, r * Fs:(r + 1) * Fs].contiguous(), t, DEV) for r in range(tp)]
+    wn = DeviceWeight.from_dense(w_next, t, DEV)
+    from distributed_llm_pipeline_b200.gguf.quants import dequantize, quantize
+    import numpy as np
+    deq = lambda m: torch.from_numpy(dequantize(quantize(m.numpy(), t), t, tuple(m.shape)).astype(np.float32)).to(DEV)
+    for step in range(2):                                       # two epochs through the same site: no stale flags / data
+        for c in comms:
+            c.begin_step()
+        for r, c in enumerate(comms):                           # phase 1: every rank pushes its partial rows
+            c.gemv(shards[r], act[:, r * Fs:(r + 1) * Fs].contiguous(), 4, T, ar_out=c.ar_out(0))
+        partial_sum = sum(act[:, r * Fs:(r + 1) * Fs].float() @ deq(w_down[:, r * Fs:(r + 1) * Fs].contiguous()).T for r in range(tp))
+        h_ref = h + partial_sum
+        xn = (h_ref * torch.rsqrt(h_ref.pow(2).mean(-1, keepdim=True) + 1e-5) * nw).half().float()
+        y_ref = xn @ deq(w_next).T
+        for r, c in enumerate(comms):                           # phase 2: every rank consumes
+            h_out = torch.zeros_like(h)
+            y = torch.empty(T, 256, device=DEV)
+            c.gemv(wn, h, 1, T, out=y, norm_w=nw, eps=1e-5, ar_in=c.ar_in(0, h_out))
+            assert nmse(h_ref, h_out) < 1e-6
+            assert nmse(y_ref, y) < 2e-5
+            c.check_error()
+        act = (act.float() * 0.5 + 0.1).half()
