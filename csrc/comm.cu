@@ -17,13 +17,13 @@ __global__ void bump_kernel(int* ctr) { pdl_wait(); pdl_launch_dependents(); *ct
 __global__ void __launch_bounds__(256) ar_consume_kernel(const float* __restrict__ h_in, float* __restrict__ h_out, const ArIn a, int K, int T) {
     pdl_wait();
     pdl_launch_dependents();
-    if ((int)threadIdx.x < a.tp) {
+    if ((int)threadIdx.x < a.tp && !(a.error && *reinterpret_cast<volatile int*>(a.error))) {
         const uint32_t want = (uint32_t)*a.epoch;
         const long long t0 = clock64();
         uint32_t v;
         do {
             asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(a.flags + threadIdx.x) : "memory");
-            if (clock64() - t0 > (1ll << 32)) { if (a.error) atomicExch(a.error, 1); break; }
+            if (clock64() - t0 > (1ll << 34)) { if (a.error) atomicExch(a.error, 1); break; }
         } while ((int32_t)(v - want) < 0);
     }
     __syncthreads();

@@ -26,11 +26,11 @@ __device__ __forceinline__ void st_release_sys_u32(uint32_t* p, uint32_t v) {
 }
 
 __device__ __forceinline__ void ar_wait(const ArIn& a) {
-    if ((int)threadIdx.x < a.tp) {
+    if ((int)threadIdx.x < a.tp && !(a.error && *reinterpret_cast<volatile int*>(a.error))) {
         const uint32_t want = (uint32_t)*a.epoch;
         const long long t0 = clock64();
         while ((int32_t)(ld_acquire_sys_u32(a.flags + threadIdx.x) - want) < 0) {
-            if (clock64() - t0 > (1ll << 32)) {  // ~2 s: a peer died or diverged; record and fall through
+            if (clock64() - t0 > (1ll << 34)) {  // ~9 s: a peer died or diverged; record once, later waits are skipped
                 if (a.error) atomicExch(a.error, 1);
                 break;
             }

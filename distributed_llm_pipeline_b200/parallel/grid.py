@@ -62,7 +62,8 @@ class Grid:
         return self.stage == self.pp - 1
 
 
-def init_grid(pp: int = 1, tp: int | None = None, backend: str | None = None, device: str | None = None) -> Grid:
+def init_grid(pp: int = 1, tp: int | None = None, backend: str | None = None, device: str | None = None,
+              timeout_s: float | None = None) -> Grid:
     """Initialise torch.distributed from the torchrun environment (or a single-process grid)."""
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
@@ -79,6 +80,9 @@ def init_grid(pp: int = 1, tp: int | None = None, backend: str | None = None, de
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         os.environ.setdefault("MASTER_PORT", "29511")
         kw = {"device_id": dev} if use_cuda else {}
+        timeout_s = timeout_s or float(os.environ.get("DLP_DIST_TIMEOUT_S", "600"))
+        import datetime
+        kw["timeout"] = datetime.timedelta(seconds=timeout_s)   # a dead / diverged peer surfaces as an error, not a hang
         dist.init_process_group(backend or ("nccl" if use_cuda else "gloo"), rank=rank, world_size=world, **kw)
     g = Grid(rank, world, pp, tp, dev)
     if world > 1:

@@ -26,7 +26,7 @@ def main():
     ap.add_argument("--batch", type=int, default=1)
     ap.add_argument("--tol", type=float, default=1e-3)
     a = ap.parse_args()
-    grid = init_grid(pp=a.pp, device=a.device)
+    grid = init_grid(pp=a.pp, device=a.device, timeout_s=90)
     comm = None
     if grid.tp > 1:
         if a.impl == "fused":

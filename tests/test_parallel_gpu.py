@@ -14,7 +14,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 def _torchrun(n, args, port):
     cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={n}", "--master-addr", "127.0.0.1",
            "--master-port", str(port), os.path.join(HERE, "mp_worker.py")] + args
-    return subprocess.run(cmd, capture_output=True, text=True, timeout=600)
+    return subprocess.run(cmd, capture_output=True, text=True, timeout=240)
 
 
 def _need(n):
