@@ -107,6 +107,39 @@ int dlp_ar_consume(const float* h_in, float* h_out, const dlp_ar_in* ar_in, int 
     return ar_consume(h_in, h_out, a, E, T, (cudaStream_t)stream);
 }
 
+int dlp_gemm_sp(const dlp_weight* w0, const dlp_weight* w1, const void* x, int ldx, void* y, int ldy, int epilogue, int T,
+                const dlp_gemm_coll* coll, void* stream) {
+    DLP_REQUIRE(w0 && w0->base && x, "dlp_gemm_sp: null argument");
+    GemmCollective c;
+    memset(&c, 0, sizeof(c));
+    if (coll) {
+        c.x_flags = coll->x_flags; c.x_rows_per_src = coll->x_rows_per_src; c.x_epoch = coll->x_epoch; c.error = coll->error;
+        for (int i = 0; i < 8; ++i) { c.rs_peer_buf[i] = coll->rs_peer_buf[i]; c.rs_peer_flags[i] = coll->rs_peer_flags[i]; }
+        c.rs_done = coll->rs_done; c.rs_rows = coll->rs_rows; c.rs_rank = coll->rs_rank; c.rs_tp = coll->rs_tp; c.rs_epoch = coll->rs_epoch;
+        DLP_REQUIRE(c.x_flags == nullptr || c.x_rows_per_src > 0, "dlp_gemm_sp: x_rows_per_src must be positive");
+    }
+    const int wt = w0->wtype;
+    cudaStream_t s = (cudaStream_t)stream;
+    if (wt == DLP_W_F16 || wt == DLP_W_BF16)
+        return gemm_f16(w0->base, w1 ? w1->base : nullptr, w0->K, x, ldx, y, ldy, T, w0->N, w0->K, epilogue, wt == DLP_W_BF16, 1, s,
+                        coll ? &c : nullptr);
+    const QWeight q0 = to_qw(w0);
+    QWeight q1;
+    if (w1) q1 = to_qw(w1);
+    return gemm_quant(q0, w1 ? &q1 : nullptr, wt, x, ldx, y, ldy, T, epilogue, 1, s, coll ? &c : nullptr);
+}
+
+int dlp_rs_norm_ag(const dlp_rs_norm_ag_desc* d, void* stream) {
+    DLP_REQUIRE(d && d->h_shard, "dlp_rs_norm_ag: null argument");
+    RsNormAg a;
+    memset(&a, 0, sizeof(a));
+    a.h_shard = d->h_shard; a.red_buf = d->red_buf; a.red_flags = d->red_flags; a.red_epoch = d->red_epoch;
+    a.norm_w = d->norm_w; a.eps = d->eps;
+    for (int i = 0; i < 8; ++i) { a.ag_peer_buf[i] = (__half*)d->ag_peer_buf[i]; a.ag_peer_flags[i] = d->ag_peer_flags[i]; }
+    a.ag_epoch = d->ag_epoch; a.done = d->done; a.error = d->error; a.rank = d->rank; a.tp = d->tp; a.rows = d->rows; a.E = d->E;
+    return rs_norm_ag(a, (cudaStream_t)stream);
+}
+
 int dlp_gemm_f16(const void* w0, const void* w1, int ldw, const void* x, int ldx, void* y, int ldy, int T, int N,
                  int K, int epilogue, int is_bf16, int split_k, void* stream) {
     DLP_REQUIRE(w0 && x && y, "dlp_gemm_f16: null argument");

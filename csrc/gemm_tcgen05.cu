@@ -9,6 +9,8 @@
 // accumulate / split-K reduction, SwiGLU over a gate+up accumulator pair) reads them back with
 // tcgen05.ld.  Operands arrive through TMA with the 128-byte swizzle; a 3..8 stage mbarrier ring
 // decouples the TMA warp from the single MMA-issuing thread.
+#include <string.h>
+
 #include "kernels.cuh"
 
 namespace dlp {
@@ -17,7 +19,7 @@ constexpr int GEMM_BM = 128;  // output features per CTA (UMMA M)
 constexpr int GEMM_BK = 64;   // K elements per pipeline stage (= 128 B of fp16: one swizzle atom)
 
 enum GemmEpilogue : int { EPI_STORE_F16 = 0, EPI_STORE_F32 = 1, EPI_ATOMIC_ADD_F32 = 2, EPI_SWIGLU_F16 = 3,
-                          EPI_STORE_BF16 = 4 };
+                          EPI_STORE_BF16 = 4, EPI_RS_PUSH_F32 = 5 };
 
 struct GemmParams {
     void* y;       // output [T, ldy]
@@ -25,6 +27,7 @@ struct GemmParams {
     int ldy;       // row stride of y in elements
     int epilogue;
     int k_blocks_per_split;
+    GemmCollective coll;   // fused all-gather (X side) / reduce-scatter (Y side); zero-initialised = none
 };
 
 template <int BT, int NA>
@@ -146,6 +149,20 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tm_w0, const __grid_cons
     if (warp == 0) {
         // ===== TMA producer =====
         if (lane == 0) {
+            if (p.coll.x_flags != nullptr) {
+                // all-gather -> GEMM: the token rows of this tile were pushed into our gather buffer by their owner
+                // ranks; wait for exactly those owners, then order the acquired generic-proxy view before the TMA reads
+                const int s0 = t0 / p.coll.x_rows_per_src, s1 = min(p.T - 1, t0 + BT - 1) / p.coll.x_rows_per_src;
+                const long long c0 = clock64();
+                for (int src = s0; src <= s1; ++src) {
+                    uint32_t v;
+                    do {
+                        asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p.coll.x_flags + src) : "memory");
+                        if (clock64() - c0 > (1ll << 34)) { if (p.coll.error) atomicExch(p.coll.error, 1); break; }
+                    } while ((int32_t)(v - p.coll.x_epoch) < 0);
+                }
+                fence_proxy_async_global();
+            }
             int stage = 0;
             uint32_t phase = 0;
             for (int kb = 0; kb < num_kb; ++kb) {
@@ -245,6 +262,14 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tm_w0, const __grid_cons
                                 if (NA == 2)
                                     reinterpret_cast<__half*>(p.y)[o] = __float2half_rn(silu_f(v) * __uint_as_float(r1[j]));
                                 break;
+                            case EPI_RS_PUSH_F32: {
+                                // GEMM -> reduce-scatter: token t is owned by rank t / rs_rows; our partial for it goes
+                                // straight into that rank's reduce buffer, slot [our rank][t % rs_rows][n] (NVLink store)
+                                const int owner = t / p.coll.rs_rows;
+                                float* dst = p.coll.rs_peer_buf[owner];
+                                dst[((size_t)p.coll.rs_rank * p.coll.rs_rows + (t - owner * p.coll.rs_rows)) * p.N + n] = v;
+                                break;
+                            }
                         }
                     }
                 }
@@ -255,7 +280,19 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tm_w0, const __grid_cons
     __syncthreads();
     if (warp == 1) {
         tc_fence_after();
+        __syncwarp();
         tmem_dealloc(tmem_base, Cfg::TMEM_COLS);
+    }
+    if (p.epilogue == EPI_RS_PUSH_F32 && threadIdx.x == 64) {
+        // every CTA's stores are ordered before its counter bump; the last CTA publishes this rank's epoch to all peers
+        __threadfence_system();
+        const unsigned total = gridDim.x * gridDim.y * gridDim.z;
+        if (atomicAdd(p.coll.rs_done, 1u) == total - 1) {
+            *p.coll.rs_done = 0;
+            __threadfence_system();
+            for (int pr = 0; pr < p.coll.rs_tp; ++pr)
+                asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p.coll.rs_peer_flags[pr] + p.coll.rs_rank), "r"(p.coll.rs_epoch) : "memory");
+        }
     }
 }
 
@@ -313,7 +350,7 @@ static int launch_gemm(const CUtensorMap& tw0, const CUtensorMap& tw1, const CUt
 
 // Y[T,N] (op)= X[T,K] . W0[N,K]^T  (and W1 for SwiGLU).  X/W are fp16 (is_bf16=0) or bf16 (is_bf16=1).
 int gemm_f16(const void* w0, const void* w1, int ldw, const void* x, int ldx, void* y, int ldy, int T, int N, int K,
-             int epilogue, int is_bf16, int split_k, cudaStream_t stream) {
+             int epilogue, int is_bf16, int split_k, cudaStream_t stream, const GemmCollective* coll) {
     DLP_REQUIRE(T > 0 && N > 0 && K > 0, "gemm: empty problem T=%d N=%d K=%d", T, N, K);
     DLP_REQUIRE(K % GEMM_BK == 0, "gemm: K=%d must be a multiple of %d", K, GEMM_BK);
     const int na = (epilogue == EPI_SWIGLU_F16) ? 2 : 1;
@@ -332,6 +369,10 @@ int gemm_f16(const void* w0, const void* w1, int ldw, const void* x, int ldx, vo
     DLP_REQUIRE(splits == 1 || epilogue == EPI_ATOMIC_ADD_F32, "gemm: split-K needs the atomic-add epilogue");
     if (splits > total_kb) splits = total_kb;
     GemmParams p;
+    memset(&p, 0, sizeof(p));
+    if (coll) p.coll = *coll;
+    DLP_REQUIRE(epilogue != EPI_RS_PUSH_F32 || (coll && coll->rs_rows > 0 && coll->rs_done && coll->rs_tp >= 1 && coll->rs_tp <= 8 && splits == 1),
+                "gemm: the reduce-scatter epilogue needs a collective descriptor and no split-K");
     p.y = y; p.T = T; p.N = N; p.K = K; p.ldy = ldy; p.epilogue = epilogue;
     p.k_blocks_per_split = (total_kb + splits - 1) / splits;
     splits = (total_kb + p.k_blocks_per_split - 1) / p.k_blocks_per_split;
@@ -363,7 +404,7 @@ int gemm_f16(const void* w0, const void* w1, int ldw, const void* x, int ldx, vo
 
 // Y[T,N] (op)= X[T,K] . dequant(W)[N,K]^T with the block-quant decode fused into the A-operand producer.
 int gemm_quant(const QWeight& w0, const QWeight* w1, int wtype, const void* x, int ldx, void* y, int ldy, int T, int epilogue,
-               int split_k, cudaStream_t stream) {
+               int split_k, cudaStream_t stream, const GemmCollective* coll) {
     const int N = w0.N, K = w0.K;
     DLP_REQUIRE(T > 0 && N > 0 && K > 0 && K % 256 == 0, "gemm_quant: bad problem T=%d N=%d K=%d", T, N, K);
     const int na = (epilogue == EPI_SWIGLU_F16) ? 2 : 1;
@@ -382,6 +423,10 @@ int gemm_quant(const QWeight& w0, const QWeight* w1, int wtype, const void* x, i
     DLP_REQUIRE(splits == 1 || epilogue == EPI_ATOMIC_ADD_F32, "gemm_quant: split-K needs the atomic-add epilogue");
     if (splits > total_kb) splits = total_kb;
     GemmParams p;
+    memset(&p, 0, sizeof(p));
+    if (coll) p.coll = *coll;
+    DLP_REQUIRE(epilogue != EPI_RS_PUSH_F32 || (coll && coll->rs_rows > 0 && coll->rs_done && coll->rs_tp >= 1 && coll->rs_tp <= 8 && splits == 1),
+                "gemm: the reduce-scatter epilogue needs a collective descriptor and no split-K");
     p.y = y; p.T = T; p.N = N; p.K = K; p.ldy = ldy; p.epilogue = epilogue;
     p.k_blocks_per_split = (total_kb + splits - 1) / splits;
     splits = (total_kb + p.k_blocks_per_split - 1) / p.k_blocks_per_split;

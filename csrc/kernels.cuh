@@ -36,6 +36,40 @@ struct GemvParams {
     ArOut ar_out;
 };
 
+// Collectives fused into the tcgen05 GEMM (prefill / batched decode under tensor parallelism, sequence-parallel layout):
+//   X side ("all-gather -> GEMM"): token rows [src*x_rows_per_src, +x_rows_per_src) of X were pushed by rank src into this
+//     rank's gather buffer; the TMA producer waits for x_flags[src] >= x_epoch of exactly the owners its tile touches.
+//   Y side ("GEMM -> reduce-scatter"): epilogue EPI_RS_PUSH_F32 stores the partial tile into the owner rank's reduce buffer
+//     [src rank][rs_rows][N] and the last CTA publishes rs_epoch to every peer's flag array.
+struct GemmCollective {
+    const uint32_t* x_flags;
+    int x_rows_per_src;
+    uint32_t x_epoch;
+    int* error;
+    float* rs_peer_buf[8];
+    uint32_t* rs_peer_flags[8];
+    unsigned* rs_done;
+    int rs_rows, rs_rank, rs_tp;
+    uint32_t rs_epoch;
+};
+
+// Reduce-scatter consumer + RMSNorm + all-gather producer (one CTA per owned token row), see comm.cu.
+struct RsNormAg {
+    float* h_shard;              // [rows, E] residual stream shard (updated in place)
+    const float* red_buf;        // local reduce buffer [tp][rows][E] (nullptr: nothing to reduce)
+    const uint32_t* red_flags;   // [tp]
+    uint32_t red_epoch;
+    const float* norm_w;         // nullptr: no norm / no gather (just fold the reduction into h_shard)
+    float eps;
+    __half* ag_peer_buf[8];      // peers' gather buffers [T, E] fp16
+    uint32_t* ag_peer_flags[8];
+    uint32_t ag_epoch;
+    unsigned* done;
+    int* error;
+    int rank, tp, rows, E;
+};
+int rs_norm_ag(const RsNormAg& a, cudaStream_t s);
+
 struct AttnParams {
     const __half* q;        // [nq, Hq, D]  (already scaled by 1/sqrt(D) and rotated)
     const __half* kc;       // [n_pages][Hkv][page][D]
@@ -51,9 +85,9 @@ struct AttnParams {
 
 int gemv(const GemvParams& p, int wtype, cudaStream_t stream);
 int gemm_f16(const void* w0, const void* w1, int ldw, const void* x, int ldx, void* y, int ldy, int T, int N, int K,
-             int epilogue, int is_bf16, int split_k, cudaStream_t stream);
+             int epilogue, int is_bf16, int split_k, cudaStream_t stream, const GemmCollective* coll = nullptr);
 int gemm_quant(const QWeight& w0, const QWeight* w1, int wtype, const void* x, int ldx, void* y, int ldy, int T, int epilogue,
-               int split_k, cudaStream_t stream);
+               int split_k, cudaStream_t stream, const GemmCollective* coll = nullptr);
 int dequant_rows_f32(const QWeight& w, int wtype, const int* row_ids, int n_rows, float* out, int ld_out, cudaStream_t s);
 int dequant_rows_f16(const QWeight& w, int wtype, const int* row_ids, int n_rows, __half* out, int ld_out, cudaStream_t s);
 int rmsnorm(float* h, const float* delta, const float* w, __half* out, int T, int E, float eps, cudaStream_t s);

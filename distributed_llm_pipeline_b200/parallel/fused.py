@@ -37,6 +37,20 @@ class dlp_ar_out(C.Structure):
                 ("done_counter", C.c_void_p), ("rank", C.c_int32), ("tp", C.c_int32)]
 
 
+class dlp_gemm_coll(C.Structure):
+    _fields_ = [("x_flags", C.c_void_p), ("x_rows_per_src", C.c_int32), ("x_epoch", C.c_uint32), ("error", C.c_void_p),
+                ("rs_peer_buf", C.c_void_p * 8), ("rs_peer_flags", C.c_void_p * 8), ("rs_done", C.c_void_p),
+                ("rs_rows", C.c_int32), ("rs_rank", C.c_int32), ("rs_tp", C.c_int32), ("rs_epoch", C.c_uint32)]
+
+
+class dlp_rs_norm_ag_desc(C.Structure):
+    _fields_ = [("h_shard", C.c_void_p), ("red_buf", C.c_void_p), ("red_flags", C.c_void_p), ("red_epoch", C.c_uint32),
+                ("pad0", C.c_uint32), ("norm_w", C.c_void_p), ("eps", C.c_float), ("pad1", C.c_uint32),
+                ("ag_peer_buf", C.c_void_p * 8), ("ag_peer_flags", C.c_void_p * 8), ("ag_epoch", C.c_uint32), ("pad2", C.c_uint32),
+                ("done", C.c_void_p), ("error", C.c_void_p), ("rank", C.c_int32), ("tp", C.c_int32), ("rows", C.c_int32),
+                ("E", C.c_int32)]
+
+
 class FusedComm(NcclComm):
     fused = True
 
@@ -67,6 +81,10 @@ class FusedComm(NcclComm):
         L.dlp_ipc_export.argtypes = [vp, vp]
         L.dlp_ipc_import.restype = i32
         L.dlp_ipc_import.argtypes = [vp, C.POINTER(vp)]
+        L.dlp_gemm_sp.restype = i32
+        L.dlp_gemm_sp.argtypes = [W, W, vp, i32, vp, i32, i32, i32, C.POINTER(dlp_gemm_coll), vp]
+        L.dlp_rs_norm_ag.restype = i32
+        L.dlp_rs_norm_ag.argtypes = [C.POINTER(dlp_rs_norm_ag_desc), vp]
 
     # ---- set-up: one symmetric allocation per rank, handles exchanged over the process group --------------
     def setup(self, n_embd: int, n_sites: int):
@@ -127,6 +145,19 @@ class FusedComm(NcclComm):
             c.peers = [o.base for o in comms]
         return comms
 
+    @classmethod
+    def make_virtual_sp(cls, tp: int, E: int, t_max: int, device="cuda") -> list["FusedComm"]:
+        """Virtual ranks (one GPU) with the sequence-parallel gather / reduce buffers wired to each other."""
+        comms = cls.make_virtual(tp, E, 1, device)
+        for c in comms:
+            total = c.sp_layout(E, t_max)
+            c._sp_mem = torch.zeros(total, dtype=torch.uint8, device=device)
+            c.sp_base = c._sp_mem.data_ptr()
+            c._sp_state()
+        for c in comms:
+            c.sp_peers = [o.sp_base for o in comms]
+        return comms
+
     def ar_in(self, site: int, h_out: torch.Tensor) -> dlp_ar_in:
         key = (site, h_out.data_ptr())
         d = self._in.get(key)
@@ -149,6 +180,90 @@ class FusedComm(NcclComm):
             d.rank, d.tp = self.tp_rank, self.tp_size
             self._out[site] = d
         return d
+
+    # ---- sequence-parallel prefill: GEMM -> reduce-scatter, all-gather -> GEMM ---------------------------------
+    # Symmetric layout per rank:  G0 | G1 (gather buffers [Tmax, E] fp16)  R0 | R1 (reduce buffers [tp][Tmax/tp][E] fp32)
+    #                             4 flag lines of 64 B (G0, G1, R0, R1)
+    def sp_layout(self, E: int, t_max: int):
+        tp = self.tp_size
+        t_max = (t_max + tp - 1) // tp * tp
+        g_bytes = t_max * E * 2
+        r_bytes = t_max * E * 4
+        self.sp_E, self.sp_tmax = E, t_max
+        self.sp_off = {"G0": 0, "G1": g_bytes, "R0": 2 * g_bytes, "R1": 2 * g_bytes + r_bytes, "F": 2 * g_bytes + 2 * r_bytes}
+        return 2 * g_bytes + 2 * r_bytes + 4 * 64
+
+    def sp_setup(self, E: int, t_max: int):
+        total = self.sp_layout(E, t_max)
+        p = C.c_void_p()
+        _lib.check(self.lib.dlp_symm_alloc(total, C.byref(p)), "symm_alloc")
+        self.sp_base = p.value
+        handle = (C.c_char * 64)()
+        _lib.check(self.lib.dlp_ipc_export(self.sp_base, handle), "ipc_export")
+        gathered: list = [None] * self.tp_size
+        dist.all_gather_object(gathered, bytes(handle), group=self.group)
+        self.sp_peers = []
+        for r, h in enumerate(gathered):
+            if r == self.tp_rank:
+                self.sp_peers.append(self.sp_base)
+                continue
+            q = C.c_void_p()
+            _lib.check(self.lib.dlp_ipc_import((C.c_char * 64).from_buffer_copy(h), C.byref(q)), "ipc_import")
+            self.sp_peers.append(q.value)
+        self._sp_state()
+        dist.barrier(group=self.group)
+
+    def _sp_state(self):
+        self.g_epoch, self.r_epoch = [0, 0], [0, 0]
+        self.sp_done = torch.zeros(1, dtype=torch.int32, device=self.device)
+        self.sp_ready = True
+
+    def sp_gather_view(self, g: int, T: int) -> int:
+        """Device address of this rank's gather buffer g (the X operand of the next column-parallel GEMM)."""
+        return self.sp_base + self.sp_off[f"G{g}"]
+
+    def sp_norm_ag(self, h_shard: torch.Tensor, rows: int, norm_w: torch.Tensor | None, eps: float, g: int | None, red: int | None):
+        """Fold reduce buffer `red` (if any) into h_shard, RMSNorm, push fp16 rows into every peer's gather buffer `g`."""
+        from ..ops import api as ops
+        d = dlp_rs_norm_ag_desc()
+        d.h_shard = h_shard.data_ptr()
+        if red is not None:
+            d.red_buf = self.sp_base + self.sp_off[f"R{red}"]
+            d.red_flags = self.sp_base + self.sp_off["F"] + (2 + red) * 64
+            d.red_epoch = self.r_epoch[red]
+        if norm_w is not None:
+            self.g_epoch[g] += 1
+            d.norm_w, d.eps, d.ag_epoch = norm_w.data_ptr(), eps, self.g_epoch[g]
+            for r in range(self.tp_size):
+                d.ag_peer_buf[r] = self.sp_peers[r] + self.sp_off[f"G{g}"]
+                d.ag_peer_flags[r] = self.sp_peers[r] + self.sp_off["F"] + g * 64
+        d.done, d.error = self.sp_done.data_ptr(), self.error.data_ptr()
+        d.rank, d.tp, d.rows, d.E = self.tp_rank, self.tp_size, rows, self.sp_E
+        _lib.check(self.lib.dlp_rs_norm_ag(C.byref(d), torch.cuda.current_stream().cuda_stream), "rs_norm_ag")
+        ops._count()
+
+    def sp_gemm(self, w, x, ldx: int, T: int, rows: int, epilogue: int, y: torch.Tensor | None = None, w_up=None,
+                x_from_g: int | None = None, rs_to: int | None = None):
+        """tcgen05 GEMM with the collective fused in: X from gather buffer `x_from_g` (waits per owner) and / or the
+        reduce-scatter push epilogue into reduce buffer `rs_to` of the owner ranks.  `x` is a tensor or a device address."""
+        from ..ops import api as ops
+        c = dlp_gemm_coll()
+        c.error = self.error.data_ptr()
+        if x_from_g is not None:
+            c.x_flags = self.sp_base + self.sp_off["F"] + x_from_g * 64
+            c.x_rows_per_src, c.x_epoch = rows, self.g_epoch[x_from_g]
+        if rs_to is not None:
+            self.r_epoch[rs_to] += 1
+            for r in range(self.tp_size):
+                c.rs_peer_buf[r] = self.sp_peers[r] + self.sp_off[f"R{rs_to}"]
+                c.rs_peer_flags[r] = self.sp_peers[r] + self.sp_off["F"] + (2 + rs_to) * 64
+            c.rs_done, c.rs_rows, c.rs_rank, c.rs_tp, c.rs_epoch = self.sp_done.data_ptr(), rows, self.tp_rank, self.tp_size, self.r_epoch[rs_to]
+        xp = x if isinstance(x, int) else x.data_ptr()
+        _lib.check(self.lib.dlp_gemm_sp(w.ref(), w_up.ref() if w_up is not None else None, xp, ldx, None if y is None else y.data_ptr(),
+                                        0 if y is None else y.stride(0), epilogue, T, C.byref(c), torch.cuda.current_stream().cuda_stream),
+                   "gemm_sp")
+        ops._count()
+        return y
 
     # ---- per-step -----------------------------------------------------------------------------------
     def begin_step(self):

@@ -157,6 +157,49 @@ int dlp_gemv_tp(const dlp_weight* w0, const dlp_weight* w1, const void* x, const
                 int ldy, int out_mode, int T, const dlp_ar_in* ar_in, const dlp_ar_out* ar_out, void* stream);
 int dlp_ar_consume(const float* h_in, float* h_out, const dlp_ar_in* ar_in, int E, int T, void* stream);
 int dlp_bump(int32_t* counter, void* stream);
+/* ---- tensor-parallel prefill / batched decode: collectives fused into the tcgen05 GEMM (sequence-parallel layout) ----
+ * The residual stream is sharded by token rows (rank r owns rows [r*rows, (r+1)*rows)).
+ *   GEMM -> reduce-scatter: a row-parallel GEMM launched with epilogue DLP_EPI_RS_PUSH stores its partial tile directly
+ *     into the owner rank's reduce buffer [src rank][rows][N] over NVLink; the last CTA publishes rs_epoch to all peers.
+ *   dlp_rs_norm_ag: the owner folds the tp partials into its residual shard, applies RMSNorm and stores the fp16 rows into
+ *     every peer's gather buffer [T][E]; the last CTA publishes ag_epoch.
+ *   all-gather -> GEMM: the next column-parallel GEMM reads X from the gather buffer; its TMA producer waits, tile by tile,
+ *     only for the owners whose rows the tile covers (x_flags[src] >= x_epoch).
+ * ref: no counterpart kernel - the reference broadcasts and gathers around every split matmul through one hub GPU
+ * (ggml-cuda/ggml-cuda.cu:1451-1769). */
+enum { DLP_EPI_RS_PUSH = 5 };
+typedef struct dlp_gemm_coll {
+    const uint32_t* x_flags;     /* NULL: X is local */
+    int32_t x_rows_per_src;
+    uint32_t x_epoch;
+    int32_t* error;
+    float* rs_peer_buf[8];
+    uint32_t* rs_peer_flags[8];
+    uint32_t* rs_done;           /* local scratch counter, zero-initialised */
+    int32_t rs_rows, rs_rank, rs_tp;
+    uint32_t rs_epoch;
+} dlp_gemm_coll;
+typedef struct dlp_rs_norm_ag_desc {
+    float* h_shard;
+    const float* red_buf;        /* NULL: nothing to reduce (first layer) */
+    const uint32_t* red_flags;
+    uint32_t red_epoch;
+    uint32_t pad0;
+    const float* norm_w;         /* NULL: only fold the reduction into h_shard */
+    float eps;
+    uint32_t pad1;
+    void* ag_peer_buf[8];
+    uint32_t* ag_peer_flags[8];
+    uint32_t ag_epoch;
+    uint32_t pad2;
+    uint32_t* done;
+    int32_t* error;
+    int32_t rank, tp, rows, E;
+} dlp_rs_norm_ag_desc;
+/* x fp16 [T, ldx]; epilogue: 0 f16, 1 f32, 2 atomic add f32, 3 SwiGLU f16 (w1 = up), 5 reduce-scatter push (y unused). */
+int dlp_gemm_sp(const dlp_weight* w0, const dlp_weight* w1, const void* x, int ldx, void* y, int ldy, int epilogue, int T,
+                const dlp_gemm_coll* coll, void* stream);
+int dlp_rs_norm_ag(const dlp_rs_norm_ag_desc* d, void* stream);
 /* symmetric memory plumbing (set-up time only; these do allocate / synchronise) */
 int dlp_symm_alloc(size_t bytes, void** ptr);
 int dlp_symm_free(void* ptr);

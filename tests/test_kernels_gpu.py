@@ -267,3 +267,48 @@ def test_fused_allreduce_protocol_virtual_ranks(t, T):
             assert nmse(y_ref, y) < 2e-5
             c.check_error()
         act = (act.float() * 0.5 + 0.1).half()
+
+
+@pytest.mark.parametrize("t", [GGMLType.F16, GGMLType.Q8_0])
+@pytest.mark.parametrize("T", [64, 200])
+def test_fused_gemm_reduce_scatter_allgather_virtual_ranks(t, T):
+    """Sequence-parallel prefill pair on 4 virtual ranks (one GPU, phases launched rank by rank):
+    row-parallel GEMM --RS push--> owners' reduce buffers --rs_norm_ag--> everyone's gather buffer --AG wait--> GEMM."""
+    from distributed_llm_pipeline_b200.parallel.fused import FusedComm
+    from distributed_llm_pipeline_b200.gguf.quants import dequantize, quantize
+    import numpy as np
+    tp, E, F, N2 = 4, 512, 1024, 384
+    Tp = (T + tp - 1) // tp * tp
+    rows = Tp // tp
+    comms = FusedComm.make_virtual_sp(tp, E, Tp)
+    g = torch.Generator().manual_seed(21)
+    w_down = torch.randn(E, F, generator=g) * 0.05
+    w_next = torch.randn(N2, E, generator=g) * 0.05
+    nw = (torch.rand(E, generator=g) + 0.5).to(DEV)
+    act = torch.zeros(Tp, F)
+    act[:T] = torch.randn(T, F, generator=g)
+    act = act.half().to(DEV)
+    h_full = torch.zeros(Tp, E)
+    h_full[:T] = torch.randn(T, E, generator=g)
+    h_full = h_full.to(DEV)
+    Fs = F // tp
+    deq = lambda m: torch.from_numpy(dequantize(quantize(m.numpy(), t), t, tuple(m.shape)).astype(np.float32)).to(DEV)
+    shards = [DeviceWeight.from_dense(w_down[:, r * Fs:(r + 1) * Fs].contiguous(), t, DEV) for r in range(tp)]
+    wn = DeviceWeight.from_dense(w_next, t, DEV)
+    h_sh = [h_full[r * rows:(r + 1) * rows].clone() for r in range(tp)]
+    for rep in range(2):        # twice through the same buffers: epochs advance, nothing stale is read
+        for r, c in enumerate(comms):      # phase 1: row-parallel GEMM, partial tiles pushed to the owner ranks
+            c.sp_gemm(shards[r], act[:, r * Fs:(r + 1) * Fs].contiguous(), Fs, Tp, rows, 5, rs_to=0)
+        for r, c in enumerate(comms):      # phase 2: owners reduce + norm + push their rows into every gather buffer
+            c.sp_norm_ag(h_sh[r], rows, nw, 1e-5, g=0, red=0)
+        partial = sum(act[:, r * Fs:(r + 1) * Fs].float() @ deq(w_down[:, r * Fs:(r + 1) * Fs].contiguous()).T for r in range(tp))
+        h_full = h_full + partial
+        xn = (h_full * torch.rsqrt(h_full.pow(2).mean(-1, keepdim=True) + 1e-5) * nw).half().float()
+        y_ref = xn @ deq(w_next).T
+        for r, c in enumerate(comms):      # phase 3: column-parallel GEMM reads the gathered X (waits per owner flag)
+            assert nmse(h_full[r * rows:(r + 1) * rows], h_sh[r]) < 1e-6
+            y = torch.empty(Tp, N2, device=DEV)
+            c.sp_gemm(wn, c.sp_gather_view(0, Tp), E, Tp, rows, 1, y=y, x_from_g=0)
+            assert nmse(y_ref[:T], y[:T]) < 2e-5
+            c.check_error()
+        act = (act.float() * 0.7).half()
