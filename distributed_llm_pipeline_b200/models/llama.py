@@ -106,7 +106,7 @@ class LlamaEngine:
         self.inv_freq = rope_inv_freq(cfg, weights.rope_freqs.cpu() if weights.rope_freqs is not None else None).to(dev)
         self.seqs: dict[int, Sequence] = {}
         self._free_sids = list(range(max_seqs - 1, -1, -1))
-        M = self.max_tokens
+        M = self.max_tokens + 8   # head-room: the sequence-parallel path pads T up to a multiple of tp
         f16, f32, i32 = torch.float16, torch.float32, torch.int32
         qkv_dim = (self.Hq + 2 * self.Hkv) * self.D
         self.h = torch.zeros(M, self.E, dtype=f32, device=dev)
@@ -116,6 +116,11 @@ class LlamaEngine:
                 self.comm.setup(self.E, 2 * len(weights.layer_range))
             self.hb = [self.h, torch.zeros(4, self.E, dtype=f32, device=dev)]   # ping-pong residual (decode rows only)
             self.cur, self.pending = 0, None
+            tp = self.comm.tp_size
+            if not getattr(self.comm, "sp_ready", False):
+                self.comm.sp_setup(self.E, M)
+            self.h_sh = torch.zeros(M // tp + 2, self.E, dtype=f32, device=dev)   # token-sharded residual (SP prefill)
+            self.G = [self.comm.sp_tensor(g) for g in (0, 1)]                            # gather buffers as fp16 [Tmax, E] views
         self.delta = torch.zeros(M, self.E, dtype=f32, device=dev)
         self.xn = torch.zeros(M, self.E, dtype=f16, device=dev)
         self.qkv32 = torch.zeros(min(M, 4), qkv_dim, dtype=f32, device=dev)
@@ -295,6 +300,57 @@ class LlamaEngine:
         for il in self.w.layer_range:
             self._layer(il, T, attn_fn)
 
+    def _forward_sp(self, T: int, attn_fn, logits_row: int | None):
+        """Tensor-parallel forward for T > 4 tokens in the sequence-parallel layout (parallel/fused.py): the residual
+        stream is sharded by token rows; every row-parallel GEMM pushes its partial tiles to the owner ranks from its
+        epilogue (GEMM -> reduce-scatter), the owners fold + RMSNorm + push fp16 rows to everyone (all-gather), and the
+        next column-parallel GEMM's TMA producer consumes the gathered rows as their flags arrive.  No NCCL call."""
+        c, cfg, w = self.comm, self.cfg, self.w
+        tp, rank = c.tp_size, c.tp_rank
+        Tp = (T + tp - 1) // tp * tp
+        rows = Tp // tp
+        r0 = rank * rows
+        nv = max(0, min(T, r0 + rows) - r0)          # valid (non-padding) rows of this rank's shard
+        hs = self.h_sh[:rows]
+        if nv < rows:
+            hs[nv:].zero_()
+        if nv > 0:
+            if self.first_stage:
+                ops.dequant_rows(w.tok_embd, self.tokens[r0:r0 + nv], out=hs[:nv])
+            else:
+                hs[:nv].copy_(self.h[r0:r0 + nv])
+        if Tp > T:
+            self.att[T:Tp].zero_()
+        E, qd, Fl = self.E, self.Hq * self.D, self.F
+        pending = None
+        for il in w.layer_range:
+            lw = w.layers[il]
+            c.sp_norm_ag(hs, rows, lw.attn_norm, cfg.rms_eps, g=0, red=pending)
+            c.sp_gemm(lw.wqkv, c.sp_gather_view(0, Tp), E, Tp, rows, 0, y=self.qkv16[:Tp], x_from_g=0)
+            q = ops.rope_kv(self.qkv16[:T], self.pos[:T], self.slot[:T], self.inv_freq, self.kv.k[il], self.kv.v[il], self.Hq, self.Hkv,
+                            self.D, cfg.rope_neox, q_out=self.q[:T])
+            attn_fn(il, q, T)
+            c.sp_gemm(lw.wo, self.att[:Tp], qd, Tp, rows, 5, rs_to=0)
+            c.sp_norm_ag(hs, rows, lw.ffn_norm, cfg.rms_eps, g=1, red=0)
+            c.sp_gemm(lw.w_gate, c.sp_gather_view(1, Tp), E, Tp, rows, 3, y=self.act[:Tp], w_up=lw.w_up, x_from_g=1)
+            c.sp_gemm(lw.w_down, self.act[:Tp], Fl, Tp, rows, 5, rs_to=1)
+            pending = 1
+        if self.last_stage and logits_row is not None:
+            c.sp_norm_ag(hs, rows, w.out_norm, cfg.rms_eps, g=0, red=pending)
+            owner = logits_row // rows
+            lg = c.sp_gemm(w.lm_head, self.G[0][logits_row:logits_row + 1], E, 1, Tp, 1, y=self.logits[:1], x_from_g=0, x_owner=owner)
+            return c.allgather_logits(lg, w.vocab_range, cfg.vocab_size)
+        if self.last_stage:   # logits for every row (batched decode): all rows of the gathered, normalised stream
+            c.sp_norm_ag(hs, rows, w.out_norm, cfg.rms_eps, g=0, red=pending)
+            lg = c.sp_gemm(w.lm_head, c.sp_gather_view(0, Tp), E, T, rows, 1, y=self.logits[:T], x_from_g=0)
+            return c.allgather_logits(lg, w.vocab_range, cfg.vocab_size)
+        # pipeline hand-off: fold the last reduction, then rebuild the full [T, E] stream for the next stage
+        c.sp_norm_ag(hs, rows, None, cfg.rms_eps, g=None, red=pending)
+        full = torch.empty(tp, rows, E, dtype=torch.float32, device=self.device)
+        torch.distributed.all_gather_into_tensor(full.view(-1), hs.reshape(-1), group=c.group)
+        self.h[:T].copy_(full.view(Tp, E)[:T])
+        return None
+
     def _finish_fused(self, T: int):
         """Fold the last pending all-reduce: into the lm_head prologue (last stage) or a stand-alone consumer."""
         c, cfg = self.comm, self.cfg
@@ -338,32 +394,44 @@ class LlamaEngine:
             slot = pages[(pos // self.page_size).long()] * self.page_size + pos % self.page_size
             self.pos[:T].copy_(pos, non_blocking=True)
             self.slot[:T].copy_(slot.to(torch.int32), non_blocking=True)
+            sp = self.fused_tp and T > 4
             if self.first_stage:
                 self.tokens[:T].copy_(tokens[c0:c0 + T], non_blocking=True)
-                self._embed(T)
+                if not sp:
+                    self._embed(T)
             else:
                 self.h[:T].copy_(hidden_in[c0:c0 + T])
-            self._run_layers(T, self._attn_prefill_for(sid, pos0))
+            if sp:
+                sp_logits = self._forward_sp(T, self._attn_prefill_for(sid, pos0), T - 1)
+            else:
+                self._run_layers(T, self._attn_prefill_for(sid, pos0))
             seq.length = pos0 + T
             if not self.last_stage:
                 outs.append(self.h[:T].clone())
         self.seq_len_dev[sid] = seq.length
         if not self.last_stage:
             return torch.cat(outs, 0)
+        if sp:
+            return sp_logits[0]
         return self._head(slice(T - 1, T), 1)[0]
 
     # ---- public: decode -------------------------------------------------------------------------
     def _decode_body(self, B: int, sample: bool):
         """One decode step for the sequence slots listed in self.active[:B]; everything stays on the device."""
         ops.advance(self.seq_len_dev, self.active, self.pos, self.slot, self.kv_len, self.kv.block_table, self.page_size, B)
-        if self.first_stage:
-            self._embed(B, self.next_tok[:B])  # input ids = previously sampled (or host-provided) tokens
         fused = self.fused_tp and B in (1, 2, 4)
-        self._run_layers(B, self._attn_decode, fused)
+        sp = self.fused_tp and B > 4
+        if sp:   # batched decode in the sequence-parallel layout (embedding happens per token shard inside)
+            self.tokens[:B].copy_(self.next_tok[:B])
+            lg = self._forward_sp(B, self._attn_decode, None)
+        else:
+            if self.first_stage:
+                self._embed(B, self.next_tok[:B])  # input ids = previously sampled (or host-provided) tokens
+            self._run_layers(B, self._attn_decode, fused)
         if fused:
             lg = self._finish_fused(B)
         if self.last_stage:
-            if not fused:
+            if not fused and not sp:
                 lg = self._head(slice(0, B), B)
             self.logits_full = lg  # full-vocab logits (gathered across TP ranks); static across graph replays
             if sample:
@@ -389,7 +457,8 @@ class LlamaEngine:
         if hidden_in is not None:
             self.h[:B].copy_(hidden_in)
         graphable = (use_graph and self.device.type == "cuda" and not self.cfg.is_moe
-                     and not getattr(self.comm, "no_graph", False))
+                     and not getattr(self.comm, "no_graph", False)
+                     and not (self.fused_tp and B > 4))   # SP path passes host-side epochs as kernel arguments
         if graphable:
             key = (B, sample) + (tuple(self.sampling.values()) if sample else ())  # sampler scalars are baked into the graph
             g = self._graphs.get(key)

@@ -218,6 +218,17 @@ class FusedComm(NcclComm):
         self.sp_done = torch.zeros(1, dtype=torch.int32, device=self.device)
         self.sp_ready = True
 
+    def sp_tensor(self, g: int) -> torch.Tensor:
+        """Zero-copy torch view ([Tmax, E] fp16) of this rank's gather buffer g."""
+        class _Mem:
+            pass
+        m = _Mem()
+        n = self.sp_tmax * self.sp_E * 2
+        m.__cuda_array_interface__ = {"shape": (n,), "typestr": "|u1", "data": (self.sp_base + self.sp_off[f"G{g}"], False), "version": 2}
+        t = torch.as_tensor(m, device=self.device)
+        self._keep = getattr(self, "_keep", []) + [m]
+        return t.view(torch.float16).view(self.sp_tmax, self.sp_E)
+
     def sp_gather_view(self, g: int, T: int) -> int:
         """Device address of this rank's gather buffer g (the X operand of the next column-parallel GEMM)."""
         return self.sp_base + self.sp_off[f"G{g}"]
@@ -243,7 +254,7 @@ class FusedComm(NcclComm):
         ops._count()
 
     def sp_gemm(self, w, x, ldx: int, T: int, rows: int, epilogue: int, y: torch.Tensor | None = None, w_up=None,
-                x_from_g: int | None = None, rs_to: int | None = None):
+                x_from_g: int | None = None, rs_to: int | None = None, x_owner: int | None = None):
         """tcgen05 GEMM with the collective fused in: X from gather buffer `x_from_g` (waits per owner) and / or the
         reduce-scatter push epilogue into reduce buffer `rs_to` of the owner ranks.  `x` is a tensor or a device address."""
         from ..ops import api as ops
@@ -252,6 +263,8 @@ class FusedComm(NcclComm):
         if x_from_g is not None:
             c.x_flags = self.sp_base + self.sp_off["F"] + x_from_g * 64
             c.x_rows_per_src, c.x_epoch = rows, self.g_epoch[x_from_g]
+            if x_owner is not None:   # X is a slice owned by a single rank: wait for that rank only
+                c.x_flags += 4 * x_owner
         if rs_to is not None:
             self.r_epoch[rs_to] += 1
             for r in range(self.tp_size):
