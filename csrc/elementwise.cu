@@ -54,7 +54,13 @@ __global__ void dense_rows_kernel(const InT* __restrict__ w, int K, const int* _
     pdl_wait();
     pdl_launch_dependents();
     const int row = row_ids ? row_ids[orow] : orow;
-    for (int k = threadIdx.x; k < K; k += blockDim.x) out[(size_t)orow * ld_out + k] = (OutT)(float)w[(size_t)row * K + k];
+    const int k = (blockIdx.y * blockDim.x + threadIdx.x) * 8;   // K is a multiple of 8 for every supported model
+    if (k + 8 <= K) {
+#pragma unroll
+        for (int j = 0; j < 8; ++j) out[(size_t)orow * ld_out + k + j] = (OutT)(float)w[(size_t)row * K + k + j];
+    } else {
+        for (int j = k; j < K; ++j) out[(size_t)orow * ld_out + j] = (OutT)(float)w[(size_t)row * K + j];
+    }
 }
 
 template <typename OutT>
@@ -62,9 +68,9 @@ static int dequant_rows_t(const QWeight& w, int wtype, const int* row_ids, int n
     DLP_REQUIRE(n_rows > 0, "dequant_rows: no rows");
     const int threads = 128;
     switch (wtype) {
-        case W_F16: DLP_CHECK_CUDA(launch_pdl(dense_rows_kernel<__half, OutT>, dim3(n_rows), dim3(256), 0, s, (const __half*)w.base, w.K, row_ids, out, ld_out)); break;
-        case W_BF16: DLP_CHECK_CUDA(launch_pdl(dense_rows_kernel<__nv_bfloat16, OutT>, dim3(n_rows), dim3(256), 0, s, (const __nv_bfloat16*)w.base, w.K, row_ids, out, ld_out)); break;
-        case W_F32: DLP_CHECK_CUDA(launch_pdl(dense_rows_kernel<float, OutT>, dim3(n_rows), dim3(256), 0, s, (const float*)w.base, w.K, row_ids, out, ld_out)); break;
+        case W_F16: DLP_CHECK_CUDA(launch_pdl(dense_rows_kernel<__half, OutT>, dim3(n_rows, (w.K / 8 + 255) / 256 + ((w.K % 2048) ? 1 : 0)), dim3(256), 0, s, (const __half*)w.base, w.K, row_ids, out, ld_out)); break;
+        case W_BF16: DLP_CHECK_CUDA(launch_pdl(dense_rows_kernel<__nv_bfloat16, OutT>, dim3(n_rows, (w.K / 8 + 255) / 256 + ((w.K % 2048) ? 1 : 0)), dim3(256), 0, s, (const __nv_bfloat16*)w.base, w.K, row_ids, out, ld_out)); break;
+        case W_F32: DLP_CHECK_CUDA(launch_pdl(dense_rows_kernel<float, OutT>, dim3(n_rows, (w.K / 8 + 255) / 256 + ((w.K % 2048) ? 1 : 0)), dim3(256), 0, s, (const float*)w.base, w.K, row_ids, out, ld_out)); break;
         case W_Q8_0: DLP_CHECK_CUDA(launch_pdl(dequant_rows_kernel<W_Q8_0, OutT>, dim3(n_rows), dim3(threads), 0, s, w, row_ids, out, ld_out)); break;
         case W_Q4_K: DLP_CHECK_CUDA(launch_pdl(dequant_rows_kernel<W_Q4_K, OutT>, dim3(n_rows), dim3(threads), 0, s, w, row_ids, out, ld_out)); break;
         case W_Q5_K: DLP_CHECK_CUDA(launch_pdl(dequant_rows_kernel<W_Q5_K, OutT>, dim3(n_rows), dim3(threads), 0, s, w, row_ids, out, ld_out)); break;
@@ -130,42 +136,44 @@ template <typename InT>
 __global__ void rope_kv_kernel(const InT* __restrict__ qkv, const int* __restrict__ pos, const int* __restrict__ slot,
                                const float* __restrict__ inv_freq, __half* __restrict__ q_out, __half* __restrict__ kc,
                                __half* __restrict__ vc, int Hq, int Hkv, int D, int n_rot, int page_size, int neox, float q_scale) {
+    // one (head, pair) per thread: grid = (T, ceil(H * D/2 / 256)) so that even a single decode token spreads over
+    // a dozen CTAs and every load is issued at once (a serial per-thread loop here is pure latency)
     const int t = blockIdx.x;
     const int H = Hq + 2 * Hkv;
+    const int half_d = D / 2;
+    const int idx = blockIdx.y * blockDim.x + threadIdx.x;
     pdl_wait();
     pdl_launch_dependents();
+    if (idx >= H * half_d) return;
     const float p = (float)pos[t];
     const int sl = slot[t];
     const int page = sl >= 0 ? sl / page_size : 0, off = sl >= 0 ? sl % page_size : 0;
     const InT* row = qkv + (size_t)t * H * D;
-    const int half_d = D / 2;
-    for (int idx = threadIdx.x; idx < H * half_d; idx += blockDim.x) {
-        const int hh = idx / half_d, i = idx % half_d;
-        int d0, d1;
-        if (neox) { d0 = i; d1 = i + n_rot / 2; } else { d0 = 2 * i; d1 = 2 * i + 1; }
-        const bool rot = hh < Hq + Hkv && (neox ? i < n_rot / 2 : 2 * i < n_rot);
-        if (neox && !rot && i >= n_rot / 2) {  // tail dims beyond the rotated span: map pair index onto them
-            d0 = n_rot + 2 * (i - n_rot / 2);
-            d1 = d0 + 1;
-        }
-        float x0 = (float)row[hh * D + d0], x1 = (float)row[hh * D + d1];
-        if (rot) {
-            float sn, cs;
-            sincosf(p * inv_freq[i], &sn, &cs);
-            const float r0 = x0 * cs - x1 * sn, r1 = x0 * sn + x1 * cs;
-            x0 = r0; x1 = r1;
-        }
-        if (hh < Hq) {
-            __half* o = q_out + ((size_t)t * Hq + hh) * D;
-            o[d0] = __float2half_rn(x0 * q_scale);
-            o[d1] = __float2half_rn(x1 * q_scale);
-        } else if (sl >= 0) {
-            const bool is_k = hh < Hq + Hkv;
-            const int kvh = is_k ? hh - Hq : hh - Hq - Hkv;
-            __half* o = (is_k ? kc : vc) + (((size_t)page * Hkv + kvh) * page_size + off) * D;
-            o[d0] = __float2half_rn(x0);
-            o[d1] = __float2half_rn(x1);
-        }
+    const int hh = idx / half_d, i = idx % half_d;
+    int d0, d1;
+    if (neox) { d0 = i; d1 = i + n_rot / 2; } else { d0 = 2 * i; d1 = 2 * i + 1; }
+    const bool rot = hh < Hq + Hkv && (neox ? i < n_rot / 2 : 2 * i < n_rot);
+    if (neox && !rot && i >= n_rot / 2) {  // tail dims beyond the rotated span: map pair index onto them
+        d0 = n_rot + 2 * (i - n_rot / 2);
+        d1 = d0 + 1;
+    }
+    float x0 = (float)row[hh * D + d0], x1 = (float)row[hh * D + d1];
+    if (rot) {
+        float sn, cs;
+        sincosf(p * inv_freq[i], &sn, &cs);
+        const float r0 = x0 * cs - x1 * sn, r1 = x0 * sn + x1 * cs;
+        x0 = r0; x1 = r1;
+    }
+    if (hh < Hq) {
+        __half* o = q_out + ((size_t)t * Hq + hh) * D;
+        o[d0] = __float2half_rn(x0 * q_scale);
+        o[d1] = __float2half_rn(x1 * q_scale);
+    } else if (sl >= 0) {
+        const bool is_k = hh < Hq + Hkv;
+        const int kvh = is_k ? hh - Hq : hh - Hq - Hkv;
+        __half* o = (is_k ? kc : vc) + (((size_t)page * Hkv + kvh) * page_size + off) * D;
+        o[d0] = __float2half_rn(x0);
+        o[d1] = __float2half_rn(x1);
     }
 }
 
@@ -174,9 +182,9 @@ int rope_kv(const void* qkv, int qkv_is_f16, const int* pos, const int* slot, co
             cudaStream_t s) {
     DLP_REQUIRE(T > 0 && D % 2 == 0 && n_rot <= D && n_rot % 2 == 0, "rope_kv: bad shape");
     if (qkv_is_f16)
-        DLP_CHECK_CUDA(launch_pdl(rope_kv_kernel<__half>, dim3(T), dim3(256), 0, s, (const __half*)qkv, pos, slot, inv_freq, q_out, kc, vc, Hq, Hkv, D, n_rot, page_size, neox, q_scale));
+        DLP_CHECK_CUDA(launch_pdl(rope_kv_kernel<__half>, dim3(T, ((Hq + 2 * Hkv) * (D / 2) + 255) / 256), dim3(256), 0, s, (const __half*)qkv, pos, slot, inv_freq, q_out, kc, vc, Hq, Hkv, D, n_rot, page_size, neox, q_scale));
     else
-        DLP_CHECK_CUDA(launch_pdl(rope_kv_kernel<float>, dim3(T), dim3(256), 0, s, (const float*)qkv, pos, slot, inv_freq, q_out, kc, vc, Hq, Hkv, D, n_rot, page_size, neox, q_scale));
+        DLP_CHECK_CUDA(launch_pdl(rope_kv_kernel<float>, dim3(T, ((Hq + 2 * Hkv) * (D / 2) + 255) / 256), dim3(256), 0, s, (const float*)qkv, pos, slot, inv_freq, q_out, kc, vc, Hq, Hkv, D, n_rot, page_size, neox, q_scale));
     return 0;
 }
 
@@ -244,9 +252,25 @@ __global__ void __launch_bounds__(1024) argmax_kernel(const float* __restrict__ 
     pdl_launch_dependents();
     float best = -INFINITY;
     int bi = 0;
-    for (int i = threadIdx.x; i < V; i += blockDim.x) {
-        const float v = row[i];
-        if (v > best) { best = v; bi = i; }
+    if ((reinterpret_cast<uintptr_t>(row) & 15) == 0) {
+        const int V4 = V / 4;
+#pragma unroll 8
+        for (int i = threadIdx.x; i < V4; i += blockDim.x) {   // 16-byte loads, 8 in flight per thread
+            const float4 v = *reinterpret_cast<const float4*>(row + 4 * i);
+            if (v.x > best) { best = v.x; bi = 4 * i; }       // within a thread indices only grow: '>' keeps the lowest
+            if (v.y > best) { best = v.y; bi = 4 * i + 1; }
+            if (v.z > best) { best = v.z; bi = 4 * i + 2; }
+            if (v.w > best) { best = v.w; bi = 4 * i + 3; }
+        }
+        for (int i = V4 * 4 + threadIdx.x; i < V; i += blockDim.x) {
+            const float v = row[i];
+            if (v > best) { best = v; bi = i; }
+        }
+    } else {
+        for (int i = threadIdx.x; i < V; i += blockDim.x) {
+            const float v = row[i];
+            if (v > best) { best = v; bi = i; }
+        }
     }
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) {
@@ -292,25 +316,38 @@ __global__ void __launch_bounds__(1024) sample_kernel(const float* __restrict__ 
     pdl_wait();
     pdl_launch_dependents();
     const int k = max(1, min(top_k <= 0 ? SAMPLE_MAX_CAND : top_k, min(V, SAMPLE_MAX_CAND)));
-    // bisection on the order-preserving integer image of the logits for the k-th largest value
-    if (threadIdx.x == 0) { s_lo = 0u; s_hi = 0xffffffffu; }
-    __syncthreads();
-    for (int it = 0; it < 32; ++it) {
-        const uint32_t lo = s_lo, hi = s_hi;
-        if (lo >= hi) break;
-        const uint32_t mid = lo + (uint32_t)(((uint64_t)hi - lo + 1) >> 1);
-        if (threadIdx.x == 0) s_count = 0;
+    // radix select (4 passes of 8 bits, most significant first) on the order-preserving integer image of the logits:
+    // after the passes `prefix` is the key of the k-th largest element
+    __shared__ int hist[256];
+    uint32_t prefix = 0, mask = 0;
+    int want = k;   // rank (from the top) still to be located inside the current prefix bucket
+    for (int pass = 0; pass < 4; ++pass) {
+        const int shift = 24 - 8 * pass;
+        for (int b = threadIdx.x; b < 256; b += blockDim.x) hist[b] = 0;
         __syncthreads();
-        int c = 0;
-        for (int i = threadIdx.x; i < V; i += blockDim.x) c += f2ord(row[i]) >= mid;
-        c = (int)warp_sum((float)c);
-        if ((threadIdx.x & 31) == 0 && c) atomicAdd(&s_count, c);
-        __syncthreads();
-        if (threadIdx.x == 0) {
-            if (s_count >= k) s_lo = mid; else s_hi = mid - 1;
+#pragma unroll 4
+        for (int i = threadIdx.x; i < V; i += blockDim.x) {
+            const uint32_t key = f2ord(row[i]);
+            if ((key & mask) == prefix) atomicAdd(&hist[(key >> shift) & 255], 1);
         }
         __syncthreads();
+        if (threadIdx.x == 0) {
+            int acc = 0, b = 255;
+            for (; b > 0; --b) {
+                if (acc + hist[b] >= want) break;
+                acc += hist[b];
+            }
+            s_lo = (uint32_t)b;
+            s_count = want - acc;
+        }
+        __syncthreads();
+        prefix |= s_lo << shift;
+        mask |= 0xFFu << shift;
+        want = s_count;
+        __syncthreads();
     }
+    if (threadIdx.x == 0) s_lo = prefix;
+    __syncthreads();
     const uint32_t thr = s_lo;  // largest threshold with count(>= thr) >= k
     if (threadIdx.x == 0) s_n = 0;
     __syncthreads();

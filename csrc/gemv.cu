@@ -6,6 +6,8 @@
 // Differences by design: activations stay fp16/fp32 (no q8_1 activation quantise pass), RMSNorm is fused
 // into the prologue (each CTA normalises x once into shared memory), the residual add is fused into the
 // epilogue, and every lane keeps 8 x 16-byte weight loads in flight (two row streams x 4-deep unroll).
+#include <stdlib.h>
+
 #include "kernels.cuh"
 
 namespace dlp {
@@ -212,6 +214,185 @@ __global__ void __launch_bounds__(256) gemv_dense_kernel(const GemvParams p) {
     if (p.out_mode == GV_PUSH_F32) ar_signal(p.ar_out);
 }
 
+
+// ---- dense weights, bulk-async pipelined variant (the decode hot path) -----------------------------------------
+// Memory-bound mat-vecs live or die by how many bytes are in flight and how early the first byte is requested.
+// Here one elected thread streams whole groups of weight rows into a shared-memory ring with cp.async.bulk (TMA,
+// mbarrier completion): no registers are tied up by loads, 160-200 KB per SM are in flight, and the first S stages
+// are requested *before* griddepcontrol.wait - i.e. while the previous kernel is still draining - and before the
+// RMSNorm prologue.  Eight consumer warps take the rows of a stage out of shared memory (R rows per stage, 8/R warps
+// per row splitting K), reduce across warps through a small per-stage partial array and apply the fused epilogue.
+__device__ __forceinline__ void bulk_g2s(void* smem_dst, const void* gsrc, uint32_t bytes, uint64_t* bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 ::"r"(smem_u32(smem_dst)), "l"(gsrc), "r"(bytes), "r"(smem_u32(bar)) : "memory");
+}
+
+struct BulkCfg { int R; int S; int n_groups; };   // rows per stage, ring depth, total row groups
+
+template <int NT, bool BF16>
+__global__ void __launch_bounds__(288, 1) gemv_bulk_kernel(const GemvParams p, const BulkCfg cfg) {
+    extern __shared__ __align__(128) uint8_t gv_smem[];
+    const int K = p.w0.K, N = p.w0.N, R = cfg.R, S = cfg.S;
+    const bool dual = p.out_mode == GV_SWIGLU_F16;
+    const int nmat = dual ? 2 : 1;
+    const uint32_t row_bytes = (uint32_t)K * 2;
+    const uint32_t stage_bytes = (uint32_t)R * row_bytes * nmat;
+    __half* xs = reinterpret_cast<__half*>(gv_smem);
+    size_t off = (size_t)NT * K * 2 + (p.ar_in.buf ? (size_t)K * 4 : 0);
+    off = (off + 127) & ~size_t(127);
+    uint8_t* ring = gv_smem + off;
+    off += (size_t)S * stage_bytes;
+    float* partials = reinterpret_cast<float*>(gv_smem + off);          // [S][8 warps][2][NT]
+    off += (size_t)S * 8 * 2 * NT * sizeof(float);
+    uint64_t* full = reinterpret_cast<uint64_t*>(gv_smem + off);
+    uint64_t* empty = full + S;
+    __shared__ float red[32];
+
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int n_local = (cfg.n_groups - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x;   // groups of this CTA
+    auto issue = [&](int it) {   // producer lane only: request row group `it` of this CTA into its ring slot
+        const int s = it % S;
+        const int row0 = ((int)blockIdx.x + it * (int)gridDim.x) * R;
+        const int nrows = min(R, N - row0);
+        const uint32_t bytes = (uint32_t)nrows * row_bytes;
+        mbar_expect_tx(&full[s], bytes * nmat);
+        uint8_t* dst = ring + (size_t)s * stage_bytes;
+        bulk_g2s(dst, p.w0.base + (size_t)row0 * row_bytes, bytes, &full[s]);
+        if (dual) bulk_g2s(dst + (size_t)R * row_bytes, p.w1.base + (size_t)row0 * row_bytes, bytes, &full[s]);
+    };
+    if (tid == 256) {
+        for (int s = 0; s < S; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], 8); }
+        mbar_fence_init();
+        for (int it = 0; it < min(S, n_local); ++it) issue(it);   // weights are static: no need to wait for the predecessor
+    }
+    pdl_wait();
+    stage_x<NT>(p, K, xs, red);   // all 288 threads (ends with __syncthreads: barrier inits are visible to everyone)
+
+    if (warp == 8) {
+        // ===== producer: refill ring slots as the consumers release them =====
+        if (lane == 0) {
+            for (int it = S; it < n_local; ++it) {
+                mbar_wait(&empty[it % S], ((it / S) - 1) & 1);
+                issue(it);
+            }
+        }
+        pdl_launch_dependents();
+    } else {
+        // ===== consumers =====
+        const int wpr = 8 / R;                       // warps per row
+        const int r = warp / wpr, sub = warp % wpr;
+        const int kspan = K / wpr, k_begin = sub * kspan;
+        for (int it = 0; it < n_local; ++it) {
+            const int s = it % S;
+            mbar_wait(&full[s], (it / S) & 1);
+            const uint8_t* st = ring + (size_t)s * stage_bytes;
+            const uint8_t* w0r = st + (size_t)r * row_bytes;
+            const uint8_t* w1r = st + (size_t)(R + r) * row_bytes;
+            float acc[2][NT];
+#pragma unroll
+            for (int m = 0; m < 2; ++m)
+#pragma unroll
+                for (int t = 0; t < NT; ++t) acc[m][t] = 0.f;
+#pragma unroll 2
+            for (int k = k_begin + lane * 8; k < k_begin + kspan; k += 256) {
+                const uint4 a = *reinterpret_cast<const uint4*>(w0r + (size_t)k * 2);
+                uint4 b = make_uint4(0, 0, 0, 0);
+                if (dual) b = *reinterpret_cast<const uint4*>(w1r + (size_t)k * 2);
+                const uint32_t aw[4] = {a.x, a.y, a.z, a.w}, bw[4] = {b.x, b.y, b.z, b.w};
+                float2 af[4], bf[4];
+#pragma unroll
+                for (int i = 0; i < 4; ++i) {
+                    af[i] = BF16 ? bf2_to_f2(aw[i]) : h2_to_f2(aw[i]);
+                    bf[i] = BF16 ? bf2_to_f2(bw[i]) : h2_to_f2(bw[i]);
+                }
+#pragma unroll
+                for (int t = 0; t < NT; ++t) {
+                    const uint4 xv = *reinterpret_cast<const uint4*>(xs + (size_t)t * K + k);
+                    const uint32_t xw[4] = {xv.x, xv.y, xv.z, xv.w};
+#pragma unroll
+                    for (int i = 0; i < 4; ++i) {
+                        const float2 xf = h2_to_f2(xw[i]);
+                        acc[0][t] = fmaf(af[i].x, xf.x, acc[0][t]);
+                        acc[0][t] = fmaf(af[i].y, xf.y, acc[0][t]);
+                        if (dual) {
+                            acc[1][t] = fmaf(bf[i].x, xf.x, acc[1][t]);
+                            acc[1][t] = fmaf(bf[i].y, xf.y, acc[1][t]);
+                        }
+                    }
+                }
+            }
+            float* pw = partials + ((size_t)s * 8 + warp) * 2 * NT;
+#pragma unroll
+            for (int m = 0; m < 2; ++m)
+#pragma unroll
+                for (int t = 0; t < NT; ++t) {
+                    const float v = warp_sum(acc[m][t]);
+                    if (lane == 0) pw[m * NT + t] = v;
+                }
+            asm volatile("bar.sync 1, 256;" ::: "memory");   // the 8 consumer warps: partials of this stage complete
+            if (tid < R * NT) {
+                const int rr = tid / NT, t = tid % NT;
+                const int row = ((int)blockIdx.x + it * (int)gridDim.x) * R + rr;
+                if (row < N) {
+                    float v0 = 0.f, v1 = 0.f;
+                    for (int wv = rr * wpr; wv < (rr + 1) * wpr; ++wv) {
+                        const float* q = partials + ((size_t)s * 8 + wv) * 2 * NT;
+                        v0 += q[t];
+                        v1 += q[NT + t];
+                    }
+                    const size_t o = (size_t)t * p.ldy + row;
+                    if (p.out_mode == GV_PUSH_F32) {
+                        for (int pr = 0; pr < p.ar_out.tp; ++pr) p.ar_out.peer_buf[pr][((size_t)p.ar_out.rank * NT + t) * N + row] = v0;
+                    } else if (p.out_mode == GV_STORE_F16) reinterpret_cast<__half*>(p.y)[o] = __float2half_rn(v0);
+                    else if (p.out_mode == GV_STORE_F32) reinterpret_cast<float*>(p.y)[o] = v0;
+                    else if (p.out_mode == GV_ADD_F32) reinterpret_cast<float*>(p.y)[o] += v0;
+                    else reinterpret_cast<__half*>(p.y)[o] = __float2half_rn(gv_silu(v0) * v1);
+                }
+            }
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&empty[s]);
+        }
+    }
+    if (p.out_mode == GV_PUSH_F32) ar_signal(p.ar_out);
+}
+
+// picks (R, S) for the bulk kernel; returns false when the shape does not fit its constraints
+static bool bulk_config(const GemvParams& p, int T, size_t fixed_smem, BulkCfg& cfg, size_t& smem) {
+    const int K = p.w0.K, N = p.w0.N;
+    const int nmat = p.out_mode == GV_SWIGLU_F16 ? 2 : 1;
+    const size_t budget = 220 * 1024;
+    for (int R = 8; R >= 1; R >>= 1) {
+        const int wpr = 8 / R;
+        if ((K / wpr) % 256 != 0 || K % wpr != 0) continue;
+        const size_t stage = (size_t)R * K * 2 * nmat;
+        if (stage > 40 * 1024 && R > 1) continue;
+        const size_t fixed = ((fixed_smem + 127) & ~size_t(127)) + 256;
+        int S = 8;
+        while (S >= 2 && fixed + (size_t)S * (stage + 8 * 2 * T * 4 + 16) > budget) --S;
+        if (S < 2) continue;
+        cfg.R = R; cfg.S = S; cfg.n_groups = (N + R - 1) / R;
+        smem = fixed + (size_t)S * (stage + 8 * 2 * T * 4 + 16);
+        return true;
+    }
+    return false;
+}
+
+template <typename Kern>
+static int launch_gemv_bulk(Kern kern, const GemvParams& p, const BulkCfg& cfg, size_t smem, cudaStream_t stream) {
+    static thread_local const void* configured[16];
+    static thread_local int n_configured = 0;
+    bool seen = false;
+    for (int i = 0; i < n_configured; ++i) seen |= configured[i] == (const void*)kern;
+    if (!seen) {
+        DLP_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+        if (n_configured < 16) configured[n_configured++] = (const void*)kern;
+    }
+    int blocks = sm_count();
+    if (blocks > cfg.n_groups) blocks = cfg.n_groups;
+    DLP_CHECK_CUDA(launch_pdl(kern, dim3(blocks), dim3(288), smem, stream, p, cfg));
+    return 0;
+}
+
 // ---- block-quantised weights ---------------------------------------------------------------------
 template <int WT, int NT>
 __global__ void __launch_bounds__(256) gemv_quant_kernel(const GemvParams p) {
@@ -325,6 +506,20 @@ int gemv(const GemvParams& p, int wtype, cudaStream_t stream) {
         case 1: return launch_gemv(KERN<__VA_ARGS__ 1>, p, smem, stream);              \
         case 2: return launch_gemv(KERN<__VA_ARGS__ 2>, p, smem, stream);              \
         default: return launch_gemv(KERN<__VA_ARGS__ 4>, p, smem, stream);             \
+    }
+    static int use_bulk = -1;
+    if (use_bulk < 0) { const char* e = getenv("DLP_GEMV_BULK"); use_bulk = (e && e[0] == '0') ? 0 : 1; }
+    if (use_bulk && (wtype == W_F16 || wtype == W_BF16)) {
+        BulkCfg cfg;
+        size_t bsm = 0;
+        if (bulk_config(p, T, smem, cfg, bsm)) {
+            const bool bf = wtype == W_BF16;
+            switch (T) {
+                case 1: return bf ? launch_gemv_bulk(gemv_bulk_kernel<1, true>, p, cfg, bsm, stream) : launch_gemv_bulk(gemv_bulk_kernel<1, false>, p, cfg, bsm, stream);
+                case 2: return bf ? launch_gemv_bulk(gemv_bulk_kernel<2, true>, p, cfg, bsm, stream) : launch_gemv_bulk(gemv_bulk_kernel<2, false>, p, cfg, bsm, stream);
+                default: return bf ? launch_gemv_bulk(gemv_bulk_kernel<4, true>, p, cfg, bsm, stream) : launch_gemv_bulk(gemv_bulk_kernel<4, false>, p, cfg, bsm, stream);
+            }
+        }
     }
     switch (wtype) {
         case W_F16:
