@@ -360,7 +360,7 @@ __global__ void __launch_bounds__(288, 1) gemv_bulk_kernel(const GemvParams p, c
 static bool bulk_config(const GemvParams& p, int T, size_t fixed_smem, BulkCfg& cfg, size_t& smem) {
     const int K = p.w0.K, N = p.w0.N;
     const int nmat = p.out_mode == GV_SWIGLU_F16 ? 2 : 1;
-    const size_t budget = 220 * 1024;
+    const size_t budget = 212 * 1024;
     for (int R = 8; R >= 1; R >>= 1) {
         const int wpr = 8 / R;
         if ((K / wpr) % 256 != 0 || K % wpr != 0) continue;
@@ -384,7 +384,7 @@ static int launch_gemv_bulk(Kern kern, const GemvParams& p, const BulkCfg& cfg, 
     bool seen = false;
     for (int i = 0; i < n_configured; ++i) seen |= configured[i] == (const void*)kern;
     if (!seen) {
-        DLP_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+        DLP_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 216 * 1024));
         if (n_configured < 16) configured[n_configured++] = (const void*)kern;
     }
     int blocks = sm_count();
