@@ -222,8 +222,6 @@ def run_ours(args) -> dict:
         res["hbm_frac_of_measured"] = round(weights.nbytes() / (ms_per_step / 1e3) / 1e9 / peaks["hbm_gbs"], 3)
     except Exception:
         pass
-    if world > 1:
-        dist.destroy_process_group()
     return res if rank == 0 else {}
 
 
@@ -299,6 +297,10 @@ def main():
     res = run_reference(args) if args.impl == "reference" else run_ours(args)
     if res:
         print(json.dumps(res), flush=True)
+    if int(os.environ.get("WORLD_SIZE", "1")) > 1:
+        # no NCCL / CUDA teardown: destroy_process_group() and plain exit were seen to block forever on this image
+        from distributed_llm_pipeline_b200.parallel.grid import shutdown
+        shutdown(0)
 
 
 if __name__ == "__main__":

@@ -508,7 +508,8 @@ int gemv(const GemvParams& p, int wtype, cudaStream_t stream) {
         default: return launch_gemv(KERN<__VA_ARGS__ 4>, p, smem, stream);             \
     }
     static int use_bulk = -1;
-    if (use_bulk < 0) { const char* e = getenv("DLP_GEMV_BULK"); use_bulk = (e && e[0] == '1') ? 1 : 0;   // experimental: slower than the register-pipelined kernel as of r1 (consumer side) }
+    // experimental: measured slower than the register-pipelined kernel in r1 (consumer side is the limit)
+    if (use_bulk < 0) { const char* e = getenv("DLP_GEMV_BULK"); use_bulk = (e && e[0] == '1') ? 1 : 0; }
     if (use_bulk && (wtype == W_F16 || wtype == W_BF16)) {
         BulkCfg cfg;
         size_t bsm = 0;

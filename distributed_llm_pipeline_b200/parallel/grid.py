@@ -96,3 +96,24 @@ def init_grid(pp: int = 1, tp: int | None = None, backend: str | None = None, de
         if g.stage < pp - 1:
             g.pp_next = g.rank + tp
     return g
+
+
+def shutdown(code: int = 0):
+    """Leave a multi-rank job without running NCCL / CUDA teardown.
+
+    Measured on this image (torch 2.11, NCCL 2.28.9, driver 580): `dist.destroy_process_group()` - and plain interpreter
+    exit with live NCCL communicators - can block forever after all useful work is done, which turns a 3-second job into a
+    hung box.  All ranks synchronise once more, flush their output and then leave with os._exit()."""
+    import sys
+    try:
+        if dist.is_initialized() and dist.get_world_size() > 1:
+            dist.barrier()
+        if torch.cuda.is_available():
+            torch.cuda.synchronize()
+    except Exception:
+        pass
+    sys.stdout.flush()
+    sys.stderr.flush()
+    if dist.is_initialized() and dist.get_world_size() > 1:
+        os._exit(code)
+    sys.exit(code)

@@ -75,10 +75,8 @@ def main():
     if grid.rank == 0:
         print(f"MP_RESULT worst_nmse={float(res):.3e} world={grid.world} pp={grid.pp} tp={grid.tp} impl={a.impl}")
     ok = float(res) < a.tol
-    if grid.world > 1:
-        dist.barrier()
-        dist.destroy_process_group()
-    sys.exit(0 if ok else 1)
+    from distributed_llm_pipeline_b200.parallel.grid import shutdown
+    shutdown(0 if ok else 1)
 
 
 if __name__ == "__main__":

@@ -117,7 +117,8 @@ def main():
         print(f"[{RANK}] fused graph decode ok {float(b[0, 0]):.4f} err flag {int(comm2.error.item())}", flush=True)
     dist.barrier()
     print(f"[{RANK}] DIAG DONE", flush=True)
-    dist.destroy_process_group()
+    from distributed_llm_pipeline_b200.parallel.grid import shutdown
+    shutdown(0)
 
 
 if __name__ == "__main__":

@@ -127,9 +127,8 @@ def main(argv=None):
             for r in rows:
                 print(f"| {meta['model']} | {w.nbytes() / 2**30:.2f} GiB/rank | {grid.pp} x {grid.tp} | {r['test']} | {r['avg_ts']:.2f} ± {r['stddev_ts']:.2f} |")
     if grid.world > 1:
-        import torch.distributed as dist
-        dist.barrier()
-        dist.destroy_process_group()
+        from distributed_llm_pipeline_b200.parallel.grid import shutdown
+        shutdown(0)
 
 
 if __name__ == "__main__":
