@@ -477,6 +477,7 @@ class LlamaEngine:
         # warm-up (also lets every kernel set its attributes), then roll back the bookkeeping it advanced
         saved = self.seq_len_dev.clone()
         saved_ctr = self.step_ctr.clone()
+        saved_h = self.h[:B].clone()   # non-first stages consume their input hidden state in place: the warm-up must not eat it
         s = torch.cuda.Stream()
         s.wait_stream(torch.cuda.current_stream())
         with torch.cuda.stream(s):
@@ -484,6 +485,7 @@ class LlamaEngine:
         torch.cuda.current_stream().wait_stream(s)
         self.seq_len_dev.copy_(saved)
         self.step_ctr.copy_(saved_ctr)
+        self.h[:B].copy_(saved_h)
         g = torch.cuda.CUDAGraph()
         n0 = ops.launch_count
         with torch.cuda.graph(g):
