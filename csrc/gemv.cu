@@ -215,7 +215,163 @@ __global__ void __launch_bounds__(256) gemv_dense_kernel(const GemvParams p) {
 }
 
 
-// ---- dense weights, bulk-async pipelined variant (the decode hot path) -----------------------------------------
+
+// ---- dense weights, v3: balanced row ranges + in-block dynamic units + register double buffering ---------------------
+// ncu on v1 (profiles/r1_ncu_*): the small matrices of a decode step (QKV 50 MB, attn-out 34 MB, down 118 MB) ran at
+// 29-49 % of DRAM throughput because (a) the grid used 0.43-0.65 of the resident CTA slots, (b) each warp walked its rows
+// in 4-14 dependent load rounds and (c) nothing was requested until the RMSNorm prologue had finished.  v3:
+//   * every CTA owns a contiguous, equally sized row range (+-1 row), so the machine is filled whatever N is;
+//   * the range is cut into units of 2 rows x (256*U) columns = one "round" of U 16-byte loads per row and lane; warps
+//     take units from a shared-memory counter, always holding the *next* unit's loads in a second register set while
+//     they reduce the current one - the load stream never waits for the math;
+//   * the first unit is requested before griddepcontrol.wait and before the prologue;
+//   * per-unit partial sums go to shared memory and are combined in a fixed order (deterministic) after one barrier.
+template <int NT, bool BF16, int U>
+__global__ void __launch_bounds__(256, 2) gemv_dense_v3_kernel(const GemvParams p) {
+    extern __shared__ __align__(16) uint8_t gv_smem[];
+    const int K = p.w0.K, N = p.w0.N;
+    constexpr int KCW = 256 * U;               // columns per unit
+    const int KC = K / KCW;                    // K chunks per row (host guarantees divisibility)
+    const bool dual = p.out_mode == GV_SWIGLU_F16;
+    const int rpu = dual ? 1 : 2;              // rows per unit (dual: one gate row + the matching up row)
+    __half* xs = reinterpret_cast<__half*>(gv_smem);
+    size_t off = (size_t)NT * K * 2 + (p.ar_in.buf ? (size_t)K * 4 : 0);
+    off = (off + 15) & ~size_t(15);
+    float* partial = reinterpret_cast<float*>(gv_smem + off);   // [n_groups][KC][2][NT]
+    __shared__ float red[32];
+    __shared__ int next_unit;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+
+    // balanced contiguous row range of this CTA (in units of rpu rows)
+    const int groups_total = (N + rpu - 1) / rpu;
+    const int g_lo = (int)(((long long)groups_total * blockIdx.x) / gridDim.x);
+    const int g_hi = (int)(((long long)groups_total * (blockIdx.x + 1)) / gridDim.x);
+    const int n_units = (g_hi - g_lo) * KC;
+
+    uint4 buf[2][2][U];   // [double buffer][stream][load]
+    auto issue = [&](int u, int b) {
+        const int g = g_lo + u / KC, c = u % KC;
+        const int row = g * rpu;
+        const uint8_t* s0 = p.w0.base + ((size_t)row * K + (size_t)c * KCW + lane * 8) * 2;
+        const uint8_t* s1 = dual ? p.w1.base + ((size_t)row * K + (size_t)c * KCW + lane * 8) * 2
+                                 : p.w0.base + ((size_t)min(row + 1, N - 1) * K + (size_t)c * KCW + lane * 8) * 2;
+#pragma unroll
+        for (int i = 0; i < U; ++i) {
+            buf[b][0][i] = ldg_nc_v4(s0 + (size_t)i * 512);
+            buf[b][1][i] = ldg_nc_v4(s1 + (size_t)i * 512);
+        }
+    };
+    auto reduce = [&](int u, int b) {
+        const int g = u / KC, c = u % KC;
+        float acc[2][NT];
+#pragma unroll
+        for (int m = 0; m < 2; ++m)
+#pragma unroll
+            for (int t = 0; t < NT; ++t) acc[m][t] = 0.f;
+#pragma unroll
+        for (int i = 0; i < U; ++i) {
+            float2 wf[2][4];
+#pragma unroll
+            for (int m = 0; m < 2; ++m) {
+                const uint32_t ww[4] = {buf[b][m][i].x, buf[b][m][i].y, buf[b][m][i].z, buf[b][m][i].w};
+#pragma unroll
+                for (int j = 0; j < 4; ++j) wf[m][j] = BF16 ? bf2_to_f2(ww[j]) : h2_to_f2(ww[j]);
+            }
+#pragma unroll
+            for (int t = 0; t < NT; ++t) {
+                const uint4 xv = *reinterpret_cast<const uint4*>(xs + (size_t)t * K + (size_t)c * KCW + i * 256 + lane * 8);
+                const uint32_t xw[4] = {xv.x, xv.y, xv.z, xv.w};
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                    const float2 xf = h2_to_f2(xw[j]);
+#pragma unroll
+                    for (int m = 0; m < 2; ++m) {
+                        acc[m][t] = fmaf(wf[m][j].x, xf.x, acc[m][t]);
+                        acc[m][t] = fmaf(wf[m][j].y, xf.y, acc[m][t]);
+                    }
+                }
+            }
+        }
+        float* dst = partial + ((size_t)g * KC + c) * 2 * NT;
+#pragma unroll
+        for (int m = 0; m < 2; ++m)
+#pragma unroll
+            for (int t = 0; t < NT; ++t) {
+                const float v = warp_sum(acc[m][t]);
+                if (lane == 0) dst[m * NT + t] = v;
+            }
+    };
+
+    int u = warp;                              // the first round is assigned statically so that it can start right now
+    if (threadIdx.x == 0) next_unit = 8;
+    if (u < n_units) issue(u, 0);              // weights are static: requested before the predecessor has finished
+    pdl_wait();
+    stage_x<NT>(p, K, xs, red);                // (ends with __syncthreads: next_unit is visible)
+
+    while (u < n_units) {                      // software pipeline, unrolled by two for static register indexing
+        int un = 0;
+        if (lane == 0) un = atomicAdd(&next_unit, 1);
+        un = __shfl_sync(0xffffffffu, un, 0);
+        if (un < n_units) issue(un, 1);
+        reduce(u, 0);
+        if (un >= n_units) break;
+        int u2 = 0;
+        if (lane == 0) u2 = atomicAdd(&next_unit, 1);
+        u2 = __shfl_sync(0xffffffffu, u2, 0);
+        if (u2 < n_units) issue(u2, 0);
+        reduce(un, 1);
+        u = u2;
+    }
+    pdl_launch_dependents();
+    __syncthreads();
+    // fixed-order combination of the K-chunk partials + fused epilogue
+    const int n_rows = (g_hi - g_lo) * rpu;
+    for (int idx = threadIdx.x; idx < n_rows * NT; idx += blockDim.x) {
+        const int rl = idx / NT, t = idx % NT;
+        const int g = rl / rpu, m = dual ? 0 : (rl % rpu);
+        const int row = (g_lo + g) * rpu + (dual ? 0 : m);
+        if (row >= N) continue;
+        float v0 = 0.f, v1 = 0.f;
+        for (int c = 0; c < KC; ++c) {
+            const float* q = partial + ((size_t)g * KC + c) * 2 * NT;
+            v0 += q[m * NT + t];
+            if (dual) v1 += q[NT + t];
+        }
+        const size_t o = (size_t)t * p.ldy + row;
+        if (p.out_mode == GV_PUSH_F32) {
+            for (int pr = 0; pr < p.ar_out.tp; ++pr) p.ar_out.peer_buf[pr][((size_t)p.ar_out.rank * NT + t) * N + row] = v0;
+        } else if (p.out_mode == GV_STORE_F16) reinterpret_cast<__half*>(p.y)[o] = __float2half_rn(v0);
+        else if (p.out_mode == GV_STORE_F32) reinterpret_cast<float*>(p.y)[o] = v0;
+        else if (p.out_mode == GV_ADD_F32) reinterpret_cast<float*>(p.y)[o] += v0;
+        else reinterpret_cast<__half*>(p.y)[o] = __float2half_rn(gv_silu(v0) * v1);
+    }
+    if (p.out_mode == GV_PUSH_F32) ar_signal(p.ar_out);
+}
+
+template <typename Kern>
+static int launch_gemv_v3(Kern kern, const GemvParams& p, int U, size_t x_smem, cudaStream_t stream) {
+    static thread_local const void* configured[32];
+    static thread_local int n_configured = 0;
+    bool seen = false;
+    for (int i = 0; i < n_configured; ++i) seen |= configured[i] == (const void*)kern;
+    if (!seen) {
+        DLP_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
+        if (n_configured < 32) configured[n_configured++] = (const void*)kern;
+    }
+    const bool dual = p.out_mode == GV_SWIGLU_F16;
+    const int rpu = dual ? 1 : 2;
+    const int groups = (p.w0.N + rpu - 1) / rpu;
+    int blocks = sm_count() * 2;
+    if (blocks > groups) blocks = groups;
+    const int KC = p.w0.K / (256 * U);
+    const int max_groups = (groups + blocks - 1) / blocks + 1;
+    const size_t smem = ((x_smem + 15) & ~size_t(15)) + (size_t)max_groups * KC * 2 * p.T * sizeof(float);
+    DLP_REQUIRE(smem <= 100 * 1024, "gemv v3: %zu bytes of shared memory needed", smem);
+    DLP_CHECK_CUDA(launch_pdl(kern, dim3(blocks), dim3(256), smem, stream, p));
+    return 0;
+}
+
+// ---- dense weights, bulk-async pipelined variant (experimental, DLP_GEMV_BULK=1) -----------------------------------------
 // Memory-bound mat-vecs live or die by how many bytes are in flight and how early the first byte is requested.
 // Here one elected thread streams whole groups of weight rows into a shared-memory ring with cp.async.bulk (TMA,
 // mbarrier completion): no registers are tied up by loads, 160-200 KB per SM are in flight, and the first S stages
@@ -521,6 +677,22 @@ int gemv(const GemvParams& p, int wtype, cudaStream_t stream) {
                 default: return bf ? launch_gemv_bulk(gemv_bulk_kernel<4, true>, p, cfg, bsm, stream) : launch_gemv_bulk(gemv_bulk_kernel<4, false>, p, cfg, bsm, stream);
             }
         }
+    }
+    static int use_v3 = -1;
+    if (use_v3 < 0) { const char* e = getenv("DLP_GEMV_V3"); use_v3 = (e && e[0] == '0') ? 0 : 1; }
+    if (use_v3 && (wtype == W_F16 || wtype == W_BF16)) {
+        const int U = (K % 1024 == 0) ? 4 : (K % 512 == 0) ? 2 : 1;
+        const bool bf = wtype == W_BF16;
+        const size_t xsm = smem;
+#define DLP_V3(NT_, U_)                                                                                           \
+    return bf ? launch_gemv_v3(gemv_dense_v3_kernel<NT_, true, U_>, p, U_, xsm, stream)                            \
+              : launch_gemv_v3(gemv_dense_v3_kernel<NT_, false, U_>, p, U_, xsm, stream);
+        if (xsm + 8192 <= 100 * 1024) {   // x (+ partials) must fit next to a second resident CTA
+            if (T == 1) { if (U == 4) { DLP_V3(1, 4) } else if (U == 2) { DLP_V3(1, 2) } else { DLP_V3(1, 1) } }
+            if (T == 2) { if (U == 4) { DLP_V3(2, 4) } else if (U == 2) { DLP_V3(2, 2) } else { DLP_V3(2, 1) } }
+            if (T == 4) { if (U == 4) { DLP_V3(4, 4) } else if (U == 2) { DLP_V3(4, 2) } else { DLP_V3(4, 1) } }
+        }
+#undef DLP_V3
     }
     switch (wtype) {
         case W_F16:
