@@ -24,7 +24,11 @@ __global__ void __launch_bounds__(128) attn_decode_kernel(const AttnParams p) {
 
     pdl_wait();
     const int len = p.kv_len[qi];
-    const int per = (len + p.n_splits - 1) / p.n_splits;
+    // effective split count grows with the context (one split per 256 keys): a short context is handled by a single CTA
+    // that writes the final result itself; the launch shape (n_splits) stays fixed so the step can live in a CUDA graph
+    const int eff = min(p.n_splits, max(1, (len + 255) / 256));
+    if (split >= eff) return;
+    const int per = (len + eff - 1) / eff;
     const int begin = split * per, end = min(len, begin + per);
     const int* bt = p.block_table + (size_t)(p.bt_row ? p.bt_row[qi] : qi) * p.max_pages;
 
@@ -131,7 +135,7 @@ __global__ void __launch_bounds__(128) attn_decode_kernel(const AttnParams p) {
             ls += sm_l[w][g] * a;
         }
         const int hq = hq0 + g;
-        if (p.n_splits == 1) {
+        if (eff == 1) {
             p.out[((size_t)qi * p.Hq + hq) * D + d] = __float2half_rn(ls > 0.f ? acc / ls : 0.f);
         } else {
             const size_t pi = ((size_t)qi * p.Hq + hq) * p.n_splits + split;
@@ -147,11 +151,14 @@ __global__ void attn_combine_kernel(const AttnParams p) {
     const size_t pi0 = ((size_t)qi * p.Hq + hq) * p.n_splits;
     pdl_wait();
     pdl_launch_dependents();
+    const int len = p.kv_len[qi];
+    const int eff = min(p.n_splits, max(1, (len + 255) / 256));
+    if (eff == 1) return;   // the single split already wrote the final output
     float mn = -INFINITY;
-    for (int s = 0; s < p.n_splits; ++s) mn = fmaxf(mn, p.part_ml[(pi0 + s) * 2]);
+    for (int s = 0; s < eff; ++s) mn = fmaxf(mn, p.part_ml[(pi0 + s) * 2]);
     for (int d = threadIdx.x; d < D; d += blockDim.x) {
         float acc = 0.f, ls = 0.f;
-        for (int s = 0; s < p.n_splits; ++s) {
+        for (int s = 0; s < eff; ++s) {
             const float ms = p.part_ml[(pi0 + s) * 2];
             const float a = (ms == -INFINITY) ? 0.f : __expf(ms - mn);
             acc += p.part_o[(pi0 + s) * D + d] * a;

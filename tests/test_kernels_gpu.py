@@ -166,9 +166,9 @@ def _fill_cache(n_pages, Hkv, page, D, seed=0):
 @pytest.mark.parametrize("D,Hq,Hkv", [(128, 8, 2), (64, 8, 1), (128, 4, 4), (64, 6, 3)])
 @pytest.mark.parametrize("n_splits", [1, 4])
 def test_attn_paged_decode(D, Hq, Hkv, n_splits):
-    page, n_pages, max_pages = 16, 64, 12
+    page, n_pages, max_pages = 16, 200, 48
     kc, vc = _fill_cache(n_pages, Hkv, page, D)
-    lens = torch.tensor([1, 17, 100, 160], dtype=torch.int32, device=DEV)
+    lens = torch.tensor([1, 17, 300, 700], dtype=torch.int32, device=DEV)   # short: single CTA; long: split-KV + combine
     nq = lens.numel()
     bt = torch.randperm(n_pages)[: nq * max_pages].view(nq, max_pages).to(torch.int32).to(DEV)
     q = (torch.randn(nq, Hq * D, device=DEV) / math.sqrt(D)).half()

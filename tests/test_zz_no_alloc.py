@@ -48,10 +48,10 @@ def _case(seed, lens, Hq, Hkv, D, page, max_pages):
 
 def test_static_scratch_matches_workspace_entry_point_twice():
     lib = _abi()
-    Hq, Hkv, D, page, max_pages, n_splits = 8, 2, 128, 16, 12, 4
+    Hq, Hkv, D, page, max_pages, n_splits = 8, 2, 128, 16, 48, 4
     stream = torch.cuda.current_stream().cuda_stream
     # two different problems back to back: the second must not see the first one's partials
-    for seed, lens in ((1, [1, 17, 100, 160]), (2, [150, 3, 64])):
+    for seed, lens in ((1, [1, 17, 300, 700]), (2, [650, 3, 264])):   # contexts long enough that the split-KV scratch is really used
         q, kc, vc, bt, kv_len = _case(seed, lens, Hq, Hkv, D, page, max_pages)
         nq = len(lens)
         want = torch.empty(nq, Hq * D, dtype=torch.float16, device="cuda")
