@@ -24,9 +24,9 @@ __global__ void __launch_bounds__(128) attn_decode_kernel(const AttnParams p) {
 
     pdl_wait();
     const int len = p.kv_len[qi];
-    // effective split count grows with the context (one split per 256 keys): a short context is handled by a single CTA
+    // effective split count grows with the context (one split per 64 keys): a short context is handled by a single CTA
     // that writes the final result itself; the launch shape (n_splits) stays fixed so the step can live in a CUDA graph
-    const int eff = min(p.n_splits, max(1, (len + 255) / 256));
+    const int eff = min(p.n_splits, max(1, (len + 63) / 64));
     if (split >= eff) return;
     const int per = (len + eff - 1) / eff;
     const int begin = split * per, end = min(len, begin + per);
@@ -57,24 +57,36 @@ __global__ void __launch_bounds__(128) attn_decode_kernel(const AttnParams p) {
         for (int i = 0; i < DL; ++i) o[g][i] = 0.f;
     }
 
-    // warp-uniform loop bound: all 32 lanes take part in every shuffle; groups past `end` re-read the
-    // last valid token and discard the result
-    for (int tok0 = begin + warp * 4; tok0 < end; tok0 += 16) {
-        const bool valid = tok0 + grp < end;
-        const int tok = valid ? tok0 + grp : end - 1;
+    // warp-uniform loop bound: all 32 lanes take part in every shuffle; groups past `end` re-read the last valid
+    // token and discard the result.  The raw K/V rows of the *next* iteration are requested before the current one is
+    // reduced (the page lookup -> K/V load chain is pure latency otherwise).
+    constexpr int NV = DL / 8;   // 16-byte loads per lane and tensor
+    uint4 kr[NV], vr[NV], kn[NV], vn[NV];
+    auto fetch = [&](int tok0, uint4 (&kd)[NV], uint4 (&vd)[NV]) {
+        const int tok = min(tok0 + grp, end - 1);
         const int page = bt[tok / p.page_size], off = tok % p.page_size;
         const size_t base = (((size_t)page * p.Hkv + kvh) * p.page_size + off) * D + sub * DL;
+#pragma unroll
+        for (int i = 0; i < NV; ++i) {
+            kd[i] = ldg_nc_v4(p.kc + base + i * 8);
+            vd[i] = ldg_nc_v4(p.vc + base + i * 8);
+        }
+    };
+    const int t_first = begin + warp * 4;
+    if (t_first < end) fetch(t_first, kr, vr);
+    for (int tok0 = t_first; tok0 < end; tok0 += 16) {
+        const bool valid = tok0 + grp < end;
+        const bool more = tok0 + 16 < end;
+        if (more) fetch(tok0 + 16, kn, vn);
         float kf[DL], vf[DL];
 #pragma unroll
-        for (int i = 0; i < DL; i += 8) {
-            const uint4 kv = ldg_nc_v4(p.kc + base + i);
-            const uint4 vv = ldg_nc_v4(p.vc + base + i);
-            const uint32_t kw[4] = {kv.x, kv.y, kv.z, kv.w}, vw[4] = {vv.x, vv.y, vv.z, vv.w};
+        for (int i = 0; i < NV; ++i) {
+            const uint32_t kw[4] = {kr[i].x, kr[i].y, kr[i].z, kr[i].w}, vw[4] = {vr[i].x, vr[i].y, vr[i].z, vr[i].w};
 #pragma unroll
             for (int j = 0; j < 4; ++j) {
                 const float2 a = h2_to_f2(kw[j]), b = h2_to_f2(vw[j]);
-                kf[i + 2 * j] = a.x; kf[i + 2 * j + 1] = a.y;
-                vf[i + 2 * j] = b.x; vf[i + 2 * j + 1] = b.y;
+                kf[i * 8 + 2 * j] = a.x; kf[i * 8 + 2 * j + 1] = a.y;
+                vf[i * 8 + 2 * j] = b.x; vf[i * 8 + 2 * j + 1] = b.y;
             }
         }
 #pragma unroll
@@ -92,6 +104,10 @@ __global__ void __launch_bounds__(128) attn_decode_kernel(const AttnParams p) {
             l[g] = l[g] * alpha + pr;
 #pragma unroll
             for (int i = 0; i < DL; ++i) o[g][i] = fmaf(pr, vf[i], o[g][i] * alpha);
+        }
+        if (more) {
+#pragma unroll
+            for (int i = 0; i < NV; ++i) { kr[i] = kn[i]; vr[i] = vn[i]; }
         }
     }
     pdl_launch_dependents();
@@ -143,6 +159,34 @@ __global__ void __launch_bounds__(128) attn_decode_kernel(const AttnParams p) {
             if (d == 0) { p.part_ml[pi * 2] = mn; p.part_ml[pi * 2 + 1] = ls; }
         }
     }
+    if (eff == 1 || p.counters == nullptr) return;
+    // fused LSE combine: the last split CTA of this (query, kv-head group) to finish merges all partials - no second launch
+    __shared__ int is_last;
+    __threadfence();
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        int* ctr = p.counters + (size_t)qi * gridDim.y + blockIdx.y;
+        const int prev = atomicAdd(ctr, 1);
+        is_last = (prev == eff - 1);
+        if (is_last) *ctr = 0;   // ready for the next launch
+    }
+    __syncthreads();
+    if (!is_last) return;
+    __threadfence();
+    for (int idx = threadIdx.x; idx < G * D; idx += blockDim.x) {
+        const int g = idx / D, d = idx % D;
+        const size_t pi0 = ((size_t)qi * p.Hq + hq0 + g) * p.n_splits;
+        float mn = -INFINITY;
+        for (int sp = 0; sp < eff; ++sp) mn = fmaxf(mn, __ldcg(p.part_ml + (pi0 + sp) * 2));
+        float acc = 0.f, ls = 0.f;
+        for (int sp = 0; sp < eff; ++sp) {
+            const float ms = __ldcg(p.part_ml + (pi0 + sp) * 2);
+            const float a = (ms == -INFINITY) ? 0.f : __expf(ms - mn);
+            acc += __ldcg(p.part_o + (pi0 + sp) * D + d) * a;
+            ls += __ldcg(p.part_ml + (pi0 + sp) * 2 + 1) * a;
+        }
+        p.out[((size_t)qi * p.Hq + hq0 + g) * D + d] = __float2half_rn(ls > 0.f ? acc / ls : 0.f);
+    }
 }
 
 template <int D>
@@ -152,7 +196,7 @@ __global__ void attn_combine_kernel(const AttnParams p) {
     pdl_wait();
     pdl_launch_dependents();
     const int len = p.kv_len[qi];
-    const int eff = min(p.n_splits, max(1, (len + 255) / 256));
+    const int eff = min(p.n_splits, max(1, (len + 63) / 64));
     if (eff == 1) return;   // the single split already wrote the final output
     float mn = -INFINITY;
     for (int s = 0; s < eff; ++s) mn = fmaxf(mn, p.part_ml[(pi0 + s) * 2]);
@@ -176,7 +220,8 @@ static int launch_attn(const AttnParams& p, cudaStream_t s) {
     if (G == 4) DLP_CHECK_CUDA(launch_pdl(attn_decode_kernel<D, 4>, grid, dim3(128), 0, s, p));
     else if (G == 2) DLP_CHECK_CUDA(launch_pdl(attn_decode_kernel<D, 2>, grid, dim3(128), 0, s, p));
     else DLP_CHECK_CUDA(launch_pdl(attn_decode_kernel<D, 1>, grid, dim3(128), 0, s, p));
-    if (p.n_splits > 1) DLP_CHECK_CUDA(launch_pdl(attn_combine_kernel<D>, dim3(p.Hq, p.nq), dim3(D), 0, s, p));
+    if (p.n_splits > 1 && p.counters == nullptr)
+        DLP_CHECK_CUDA(launch_pdl(attn_combine_kernel<D>, dim3(p.Hq, p.nq), dim3(D), 0, s, p));
     return 0;
 }
 
@@ -431,6 +476,7 @@ int attn_paged_static(AttnParams p, int D, cudaStream_t s) {
         DLP_REQUIRE(ptr != nullptr, "attn_paged_static: cudaGetSymbolAddress returned a null address");
         dev_ptr[dev] = ptr;
     }
+    p.counters = nullptr;                // this entry point keeps the two-kernel combine
     p.part_o = ptr;                      // [nq, Hq, n_splits, D]
     p.part_ml = ptr + n_part * (size_t)D;  // [nq, Hq, n_splits, 2]
     return attn_paged(p, D, s);

@@ -221,7 +221,20 @@ int dlp_attn_paged(const void* q, const void* k_cache, const void* v_cache, cons
     AttnParams p;
     p.q = (const __half*)q; p.kc = (const __half*)k_cache; p.vc = (const __half*)v_cache;
     p.block_table = block_table; p.bt_row = bt_row; p.kv_len = kv_len; p.out = (__half*)out;
-    p.part_o = part_o; p.part_ml = part_ml;
+    p.part_o = part_o; p.part_ml = part_ml; p.counters = nullptr;
+    p.nq = nq; p.Hq = Hq; p.Hkv = Hkv; p.max_pages = max_pages; p.page_size = page_size; p.n_splits = n_splits;
+    return attn_paged(p, D, (cudaStream_t)stream);
+}
+
+int dlp_attn_paged_fused(const void* q, const void* k_cache, const void* v_cache, const int32_t* block_table,
+                         const int32_t* bt_row, const int32_t* kv_len, void* out, float* part_o, float* part_ml,
+                         int32_t* counters, int nq, int Hq, int Hkv, int D, int max_pages, int page_size, int n_splits,
+                         void* stream) {
+    DLP_REQUIRE(q && k_cache && v_cache && block_table && kv_len && out && counters, "dlp_attn_paged_fused: null argument");
+    AttnParams p;
+    p.q = (const __half*)q; p.kc = (const __half*)k_cache; p.vc = (const __half*)v_cache;
+    p.block_table = block_table; p.bt_row = bt_row; p.kv_len = kv_len; p.out = (__half*)out;
+    p.part_o = part_o; p.part_ml = part_ml; p.counters = counters;
     p.nq = nq; p.Hq = Hq; p.Hkv = Hkv; p.max_pages = max_pages; p.page_size = page_size; p.n_splits = n_splits;
     return attn_paged(p, D, (cudaStream_t)stream);
 }
@@ -233,7 +246,7 @@ int dlp_attn_paged_static(const void* q, const void* k_cache, const void* v_cach
     AttnParams p;
     p.q = (const __half*)q; p.kc = (const __half*)k_cache; p.vc = (const __half*)v_cache;
     p.block_table = block_table; p.bt_row = bt_row; p.kv_len = kv_len; p.out = (__half*)out;
-    p.part_o = nullptr; p.part_ml = nullptr;
+    p.part_o = nullptr; p.part_ml = nullptr; p.counters = nullptr;
     p.nq = nq; p.Hq = Hq; p.Hkv = Hkv; p.max_pages = max_pages; p.page_size = page_size; p.n_splits = n_splits;
     return attn_paged_static(p, D, (cudaStream_t)stream);
 }

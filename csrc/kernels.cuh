@@ -80,6 +80,7 @@ struct AttnParams {
     __half* out;            // [nq, Hq, D]
     float* part_o;          // [nq, Hq, n_splits, D]   (n_splits > 1)
     float* part_ml;         // [nq, Hq, n_splits, 2]
+    int* counters;          // [nq, Hkv * groups] zero-initialised; non-null => the last split CTA combines in-kernel
     int nq, Hq, Hkv, max_pages, page_size, n_splits;
 };
 

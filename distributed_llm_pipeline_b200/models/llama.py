@@ -142,7 +142,8 @@ class LlamaEngine:
         self.attn_splits = attn_splits if attn_splits is not None else (16 if dev.type == "cuda" else 1)
         ns = self.attn_splits
         self.attn_ws = (torch.zeros(max_seqs * self.Hq * ns * self.D, dtype=f32, device=dev),
-                        torch.zeros(max_seqs * self.Hq * ns * 2, dtype=f32, device=dev)) if ns > 1 else None
+                        torch.zeros(max_seqs * self.Hq * ns * 2, dtype=f32, device=dev),
+                        torch.zeros(max_seqs * self.Hq, dtype=i32, device=dev)) if ns > 1 else None
         self.scratch = None  # fp16 decode buffer for block-quantised weights on the GEMM path (allocated lazily)
         self._graphs: dict[tuple, torch.cuda.CUDAGraph] = {}
         self.sampling = dict(top_k=40, top_p=0.95, min_p=0.05, temp=0.0, seed=0)

@@ -213,13 +213,22 @@ def attn_paged(q: torch.Tensor, k_cache: torch.Tensor, v_cache: torch.Tensor, bl
         return res
     if out is None:
         out = torch.empty(nq, n_head * head_dim, dtype=torch.float16, device=q.device)
-    po = pm = None
+    po = pm = ctr = None
     if n_splits > 1:
         if workspace is None:
             po = torch.empty(nq * n_head * n_splits * head_dim, dtype=torch.float32, device=q.device)
             pm = torch.empty(nq * n_head * n_splits * 2, dtype=torch.float32, device=q.device)
+        elif len(workspace) == 3:   # (partials, lse, counters): combine fused into the attention kernel
+            po, pm, ctr = workspace
         else:
             po, pm = workspace
+    if ctr is not None:
+        _lib.check(_lib.load().dlp_attn_paged_fused(q.data_ptr(), k_cache.data_ptr(), v_cache.data_ptr(), block_table.data_ptr(),
+                                                    _p(bt_row), kv_len.data_ptr(), out.data_ptr(), _p(po), _p(pm), ctr.data_ptr(), nq,
+                                                    n_head, n_head_kv, head_dim, block_table.shape[1], k_cache.shape[2], n_splits,
+                                                    _stream()), "attn_paged_fused")
+        _count()
+        return out
     _lib.check(_lib.load().dlp_attn_paged(q.data_ptr(), k_cache.data_ptr(), v_cache.data_ptr(), block_table.data_ptr(),
                                           _p(bt_row), kv_len.data_ptr(), out.data_ptr(), _p(po), _p(pm), nq, n_head,
                                           n_head_kv, head_dim, block_table.shape[1], k_cache.shape[2], n_splits,

@@ -95,6 +95,14 @@ int dlp_attn_paged(const void* q, const void* k_cache, const void* v_cache, cons
                    const int32_t* bt_row, const int32_t* kv_len, void* out, float* part_o, float* part_ml, int nq,
                    int Hq, int Hkv, int D, int max_pages, int page_size, int n_splits, void* stream);
 
+/* Same, with the split-KV combine fused into the attention kernel: `counters` is an int32 array of nq * Hkv * (Hq/Hkv/G)
+ * entries (G = 4, 2 or 1 query heads per CTA; nq * Hq entries always suffice), zero-initialised once; the last split CTA of
+ * each (query, kv-head group) merges the partials and resets its counter.  One launch instead of two. */
+int dlp_attn_paged_fused(const void* q, const void* k_cache, const void* v_cache, const int32_t* block_table,
+                         const int32_t* bt_row, const int32_t* kv_len, void* out, float* part_o, float* part_ml,
+                         int32_t* counters, int nq, int Hq, int Hkv, int D, int max_pages, int page_size, int n_splits,
+                         void* stream);
+
 /* dlp_attn_paged for callers that cannot supply the split-KV workspace.  (No counterpart in the reference: it always
  * allocates its own split buffers from the backend pool.)
  * Who needs it: hosts that are not allowed to allocate device memory when they call us - a server that split all of HBM

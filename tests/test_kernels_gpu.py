@@ -175,6 +175,13 @@ def test_attn_paged_decode(D, Hq, Hkv, n_splits):
     out = ops.attn_paged(q, kc, vc, bt, lens, Hq, Hkv, D, n_splits=n_splits)
     ref = ops._attn_cpu(q.cpu(), kc.cpu(), vc.cpu(), bt.cpu(), lens.cpu(), Hq, Hkv, D)
     assert nmse(ref, out) < 5e-5
+    if n_splits > 1:   # combine fused into the attention kernel (last split CTA merges); twice: counters must self-reset
+        ws = (torch.empty(nq * Hq * n_splits * D, device=DEV), torch.empty(nq * Hq * n_splits * 2, device=DEV),
+              torch.zeros(nq * Hq, dtype=torch.int32, device=DEV))
+        for _ in range(2):
+            out2 = ops.attn_paged(q, kc, vc, bt, lens, Hq, Hkv, D, n_splits=n_splits, workspace=ws)
+            assert nmse(ref, out2) < 5e-5
+        assert int(ws[2].abs().sum()) == 0
 
 
 @pytest.mark.parametrize("D,Hq,Hkv", [(128, 8, 2), (64, 4, 2)])
