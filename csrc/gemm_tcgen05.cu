@@ -98,6 +98,39 @@ __device__ __forceinline__ void prefetch_row_slice(const QWeight& w, int row, in
     else if (WT == W_Q6_K) prefetch_l2(w.base + ((size_t)row * (w.K >> 8) + (kc >> 8)) * 128 + ((kc & 255) >> 7) * 64);
 }
 
+template <int MODE, int CH>
+__device__ __forceinline__ void epi_loop(const GemmParams& p, const uint32_t (&r0)[CH], const uint32_t (&r1)[CH], int tb, int n) {
+    if (MODE == EPI_RS_PUSH_F32) {
+        // GEMM -> reduce-scatter: token t is owned by rank t / rs_rows; our partial for it goes straight into that rank's
+        // reduce buffer, slot [our rank][t % rs_rows][n] (NVLink store).  Owner / local row advance incrementally.
+        int owner = tb / p.coll.rs_rows;
+        int local = tb - owner * p.coll.rs_rows;
+        float* dst = p.coll.rs_peer_buf[owner] + ((size_t)p.coll.rs_rank * p.coll.rs_rows + local) * p.N + n;
+#pragma unroll
+        for (int j = 0; j < CH; ++j) {
+            if (tb + j < p.T) *dst = __uint_as_float(r0[j]);
+            dst += p.N;
+            if (++local == p.coll.rs_rows) {
+                local = 0;
+                ++owner;
+                if (owner < p.coll.rs_tp) dst = p.coll.rs_peer_buf[owner] + (size_t)p.coll.rs_rank * p.coll.rs_rows * p.N + n;
+            }
+        }
+        return;
+    }
+    size_t o = (size_t)tb * p.ldy + n;
+#pragma unroll
+    for (int j = 0; j < CH; ++j, o += p.ldy) {
+        if (tb + j >= p.T) break;
+        const float v = __uint_as_float(r0[j]);
+        if (MODE == EPI_STORE_F16) reinterpret_cast<__half*>(p.y)[o] = __float2half_rn(v);
+        else if (MODE == EPI_STORE_BF16) reinterpret_cast<__nv_bfloat16*>(p.y)[o] = __float2bfloat16_rn(v);
+        else if (MODE == EPI_STORE_F32) reinterpret_cast<float*>(p.y)[o] = v;
+        else if (MODE == EPI_ATOMIC_ADD_F32) atomicAdd(reinterpret_cast<float*>(p.y) + o, v);
+        else if (MODE == EPI_SWIGLU_F16) reinterpret_cast<__half*>(p.y)[o] = __float2half_rn(silu_f(v) * __uint_as_float(r1[j]));
+    }
+}
+
 template <int BT, int NA, int AB_FMT, int WT>
 __global__ void __launch_bounds__(192, 1)
 gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tm_w0, const __grid_constant__ CUtensorMap tm_w1,
@@ -247,31 +280,16 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tm_w0, const __grid_cons
                 for (int j = 0; j < CH; ++j) { r0[j] = 0; r1[j] = 0; }
             }
             if (n < p.N) {
-#pragma unroll
-                for (int j = 0; j < CH; ++j) {
-                    const int t = t0 + c * CH + j;
-                    if (t < p.T) {
-                        const float v = __uint_as_float(r0[j]);
-                        const size_t o = (size_t)t * p.ldy + n;
-                        switch (p.epilogue) {
-                            case EPI_STORE_F16: reinterpret_cast<__half*>(p.y)[o] = __float2half_rn(v); break;
-                            case EPI_STORE_BF16: reinterpret_cast<__nv_bfloat16*>(p.y)[o] = __float2bfloat16_rn(v); break;
-                            case EPI_STORE_F32: reinterpret_cast<float*>(p.y)[o] = v; break;
-                            case EPI_ATOMIC_ADD_F32: atomicAdd(reinterpret_cast<float*>(p.y) + o, v); break;
-                            case EPI_SWIGLU_F16:
-                                if (NA == 2)
-                                    reinterpret_cast<__half*>(p.y)[o] = __float2half_rn(silu_f(v) * __uint_as_float(r1[j]));
-                                break;
-                            case EPI_RS_PUSH_F32: {
-                                // GEMM -> reduce-scatter: token t is owned by rank t / rs_rows; our partial for it goes
-                                // straight into that rank's reduce buffer, slot [our rank][t % rs_rows][n] (NVLink store)
-                                const int owner = t / p.coll.rs_rows;
-                                float* dst = p.coll.rs_peer_buf[owner];
-                                dst[((size_t)p.coll.rs_rank * p.coll.rs_rows + (t - owner * p.coll.rs_rows)) * p.N + n] = v;
-                                break;
-                            }
-                        }
-                    }
+                // one specialised store loop per epilogue (dispatch hoisted out of the per-element loop: a switch with the
+                // reduce-scatter address arithmetic inside it cost 35-50 % of the whole GEMM, see profiles/r1_gemm_ab.txt)
+                const int tb = t0 + c * CH;
+                switch (p.epilogue) {
+                    case EPI_STORE_F16: epi_loop<EPI_STORE_F16, CH>(p, r0, r1, tb, n); break;
+                    case EPI_STORE_BF16: epi_loop<EPI_STORE_BF16, CH>(p, r0, r1, tb, n); break;
+                    case EPI_STORE_F32: epi_loop<EPI_STORE_F32, CH>(p, r0, r1, tb, n); break;
+                    case EPI_ATOMIC_ADD_F32: epi_loop<EPI_ATOMIC_ADD_F32, CH>(p, r0, r1, tb, n); break;
+                    case EPI_SWIGLU_F16: if (NA == 2) epi_loop<EPI_SWIGLU_F16, CH>(p, r0, r1, tb, n); break;
+                    case EPI_RS_PUSH_F32: epi_loop<EPI_RS_PUSH_F32, CH>(p, r0, r1, tb, n); break;
                 }
             }
         }
