@@ -625,6 +625,268 @@ __global__ void __launch_bounds__(256) gemv_quant_kernel(const GemvParams p) {
     if (p.out_mode == GV_PUSH_F32) ar_signal(p.ar_out);
 }
 
+
+// ---- block-quantised weights, v3: int8 activations + dp4a, balanced / dynamic / double-buffered like the dense v3 ------
+// The fp32-decode kernel below (v1) needs ~150 instructions per 32 weights and is issue-bound (Q8_0 decoded at 43 % of
+// HBM bandwidth, no faster than fp16).  v3 quantises the (already normalised) activations once per CTA to int8 with one
+// fp32 scale per 32 values - the numerics class of the reference's q8_1 path (mmvq.cu / quantize.cu) - and reduces each
+// 32-weight chunk with 8 dp4a, so all formats stream at memory speed.  Per chunk:  w_i = scale*q_i + bias  gives
+//   sum_i w_i x_i  ~=  scale * dx * dot_int(q, xq) + bias * sum_i x_i     (the last sum is kept in fp32, exact)
+// For Q6_K the stored 6-bit value is q+32: dot_int(u, xq) - 32 * sum_int(xq) recovers the signed product exactly.
+template <int WT> struct QRaw;
+template <> struct QRaw<W_Q8_0> { uint4 a, b; float d; };
+template <> struct QRaw<W_Q4_K> { uint4 qs; float s0, s1, b0, b1; };
+template <> struct QRaw<W_Q5_K> { uint4 qs, qh; float s0, s1, b0, b1; int sh; };
+template <> struct QRaw<W_Q6_K> { uint4 ql, qh; float s0, s1; int sh; };
+
+template <int WT> __device__ __forceinline__ void qraw_load(const QWeight& w, int row, int c, QRaw<WT>& r);
+template <> __device__ __forceinline__ void qraw_load<W_Q8_0>(const QWeight& w, int row, int c, QRaw<W_Q8_0>& r) {
+    const uint8_t* qs = w.base + (size_t)row * w.K + (size_t)c * 32;
+    r.a = ldg_nc_v4(qs);
+    r.b = ldg_nc_v4(qs + 16);
+    r.d = __half2float(reinterpret_cast<const __half*>(w.aux0)[(size_t)row * (w.K >> 5) + c]);
+}
+template <> __device__ __forceinline__ void qraw_load<W_Q4_K>(const QWeight& w, int row, int c, QRaw<W_Q4_K>& r) {
+    const int blk = c >> 3, j = (c & 7) >> 1, l0 = (c & 1) * 16;
+    const uint8_t* b = w.base + ((size_t)row * (w.K >> 8) + blk) * 144;
+    const uint4 hdr = __ldg(reinterpret_cast<const uint4*>(b));
+    r.qs = ldg_nc_v4(b + 16 + j * 32 + l0);
+    const float2 dm = h2_to_f2(hdr.x);
+    int sc0, mn0, sc1, mn1;
+    scale_min_k4(hdr.y, hdr.z, hdr.w, 2 * j, sc0, mn0);
+    scale_min_k4(hdr.y, hdr.z, hdr.w, 2 * j + 1, sc1, mn1);
+    r.s0 = dm.x * sc0; r.s1 = dm.x * sc1; r.b0 = -dm.y * mn0; r.b1 = -dm.y * mn1;
+}
+template <> __device__ __forceinline__ void qraw_load<W_Q5_K>(const QWeight& w, int row, int c, QRaw<W_Q5_K>& r) {
+    const int blk = c >> 3, j = (c & 7) >> 1, l0 = (c & 1) * 16;
+    const uint8_t* b = w.base + ((size_t)row * (w.K >> 8) + blk) * 176;
+    const uint4 hdr = __ldg(reinterpret_cast<const uint4*>(b));
+    r.qh = __ldg(reinterpret_cast<const uint4*>(b + 16 + l0));
+    r.qs = ldg_nc_v4(b + 48 + j * 32 + l0);
+    const float2 dm = h2_to_f2(hdr.x);
+    int sc0, mn0, sc1, mn1;
+    scale_min_k4(hdr.y, hdr.z, hdr.w, 2 * j, sc0, mn0);
+    scale_min_k4(hdr.y, hdr.z, hdr.w, 2 * j + 1, sc1, mn1);
+    r.s0 = dm.x * sc0; r.s1 = dm.x * sc1; r.b0 = -dm.y * mn0; r.b1 = -dm.y * mn1; r.sh = 2 * j;
+}
+template <> __device__ __forceinline__ void qraw_load<W_Q6_K>(const QWeight& w, int row, int c, QRaw<W_Q6_K>& r) {
+    const int blk = c >> 3, cc = c & 7, half = cc >> 2, l0 = (cc & 3) * 16;
+    const int lq = l0 & 31, upper = l0 >> 5;
+    const size_t nblk = (size_t)row * (w.K >> 8) + blk;
+    r.ql = ldg_nc_v4(w.base + nblk * 128 + half * 64 + l0);
+    r.qh = ldg_nc_v4(w.aux0 + nblk * 64 + half * 32 + lq);
+    const int8_t* sc = reinterpret_cast<const int8_t*>(w.aux1) + nblk * 16 + half * 8 + (lq >> 4) + upper * 2;
+    const float d = __half2float(reinterpret_cast<const __half*>(w.aux2)[nblk]);
+    r.s0 = d * (float)sc[0]; r.s1 = d * (float)sc[4]; r.sh = upper * 2;
+}
+
+// element offsets of the two 16-element groups of chunk c (same mapping as load_chunk in quant.cuh)
+template <int WT> __device__ __forceinline__ void chunk_offsets(int c, int& k0, int& k1) {
+    if (WT == W_Q8_0) { k0 = c * 32; k1 = k0 + 16; }
+    else if (WT == W_Q6_K) {
+        const int blk = c >> 3, cc = c & 7, half = cc >> 2, l0 = (cc & 3) * 16;
+        k0 = blk * 256 + half * 128 + (l0 >> 5) * 32 + (l0 & 31); k1 = k0 + 64;
+    } else { k0 = (c >> 3) * 256 + ((c & 7) >> 1) * 64 + (c & 1) * 16; k1 = k0 + 32; }
+}
+
+__device__ __forceinline__ int dp4a4(const uint32_t (&q)[4], const uint4& x) {
+    int s = __dp4a((int)q[0], (int)x.x, 0);
+    s = __dp4a((int)q[1], (int)x.y, s);
+    s = __dp4a((int)q[2], (int)x.z, s);
+    return __dp4a((int)q[3], (int)x.w, s);
+}
+
+// dot of one raw chunk with token t's int8 activations; xq int8 [K], xd fp32 [K/32] scales, xs16 fp32 [K/16] exact sums
+template <int WT>
+__device__ __forceinline__ float qraw_dot(const QRaw<WT>& r, const int8_t* xq, const float* xd, const float* xs16, int k0, int k1) {
+    const uint4 xa = *reinterpret_cast<const uint4*>(xq + k0);
+    const uint4 xb = *reinterpret_cast<const uint4*>(xq + k1);
+    if constexpr (WT == W_Q8_0) {
+        const uint32_t qa[4] = {r.a.x, r.a.y, r.a.z, r.a.w}, qb[4] = {r.b.x, r.b.y, r.b.z, r.b.w};
+        const int isum = dp4a4(qa, xa) + dp4a4(qb, xb);
+        return r.d * xd[k0 >> 5] * (float)isum;
+    } else if constexpr (WT == W_Q4_K || WT == W_Q5_K) {
+        const uint32_t w4[4] = {r.qs.x, r.qs.y, r.qs.z, r.qs.w};
+        uint32_t lo[4], hi[4];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            lo[i] = w4[i] & 0x0F0F0F0Fu;
+            hi[i] = (w4[i] >> 4) & 0x0F0F0F0Fu;
+        }
+        if constexpr (WT == W_Q5_K) {
+            const uint32_t h4[4] = {r.qh.x, r.qh.y, r.qh.z, r.qh.w};
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                lo[i] |= ((h4[i] >> r.sh) & 0x01010101u) << 4;
+                hi[i] |= ((h4[i] >> (r.sh + 1)) & 0x01010101u) << 4;
+            }
+        }
+        const float d0 = r.s0 * xd[k0 >> 5] * (float)dp4a4(lo, xa);
+        const float d1 = r.s1 * xd[k1 >> 5] * (float)dp4a4(hi, xb);
+        return d0 + d1 + r.b0 * xs16[k0 >> 4] + r.b1 * xs16[k1 >> 4];
+    } else {   // Q6_K
+        const uint32_t l4[4] = {r.ql.x, r.ql.y, r.ql.z, r.ql.w}, h4[4] = {r.qh.x, r.qh.y, r.qh.z, r.qh.w};
+        uint32_t lo[4], hi[4];
+        const uint32_t ones[4] = {0x01010101u, 0x01010101u, 0x01010101u, 0x01010101u};
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            lo[i] = (l4[i] & 0x0F0F0F0Fu) | (((h4[i] >> r.sh) & 0x03030303u) << 4);
+            hi[i] = ((l4[i] >> 4) & 0x0F0F0F0Fu) | (((h4[i] >> (r.sh + 4)) & 0x03030303u) << 4);
+        }
+        const int ia = dp4a4(lo, xa) - 32 * dp4a4(ones, xa);
+        const int ib = dp4a4(hi, xb) - 32 * dp4a4(ones, xb);
+        return r.s0 * xd[k0 >> 5] * (float)ia + r.s1 * xd[k1 >> 5] * (float)ib;
+    }
+}
+
+template <int WT, int NT>
+__global__ void __launch_bounds__(256, 2) gemv_quant_v3_kernel(const GemvParams p) {
+    extern __shared__ __align__(16) uint8_t gv_smem[];
+    const int K = p.w0.K, N = p.w0.N;
+    const int nchunk = K >> 5;
+    const int KC = (nchunk + 31) >> 5;          // units of 32 chunks (1024 columns) per row; the last may be partial
+    const bool dual = p.out_mode == GV_SWIGLU_F16;
+    const int rpu = dual ? 1 : 2;
+    // shared memory: fp16 x [NT][K] (stage_x output, AR staging behind it) | int8 xq [NT][K] | xd [NT][K/32] | xs16 [NT][K/16] | partials
+    __half* xs = reinterpret_cast<__half*>(gv_smem);
+    size_t off = (size_t)NT * K * 2 + (p.ar_in.buf ? (size_t)K * 4 : 0);
+    off = (off + 15) & ~size_t(15);
+    int8_t* xq = reinterpret_cast<int8_t*>(gv_smem + off);
+    off += (size_t)NT * K;
+    float* xd = reinterpret_cast<float*>(gv_smem + off);
+    off += (size_t)NT * nchunk * 4;
+    float* xs16 = reinterpret_cast<float*>(gv_smem + off);
+    off += (size_t)NT * (K >> 4) * 4;
+    float* partial = reinterpret_cast<float*>(gv_smem + off);
+    __shared__ float red[32];
+    __shared__ int next_unit;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int groups_total = (N + rpu - 1) / rpu;
+    const int g_lo = (int)(((long long)groups_total * blockIdx.x) / gridDim.x);
+    const int g_hi = (int)(((long long)groups_total * (blockIdx.x + 1)) / gridDim.x);
+    const int n_units = (g_hi - g_lo) * KC;
+
+    QRaw<WT> buf[2][2];   // [double buffer][row stream]
+    auto issue = [&](int u, int b) {
+        const int g = g_lo + u / KC, c = (u % KC) * 32 + lane;
+        if (c >= nchunk) return;
+        const int row = g * rpu;
+        qraw_load<WT>(p.w0, row, c, buf[b][0]);
+        if (dual) qraw_load<WT>(p.w1, row, c, buf[b][1]);
+        else qraw_load<WT>(p.w0, min(row + 1, N - 1), c, buf[b][1]);
+    };
+    auto reduce = [&](int u, int b) {
+        const int g = u / KC, cu = u % KC, c = cu * 32 + lane;
+        float acc[2][NT];
+#pragma unroll
+        for (int m = 0; m < 2; ++m)
+#pragma unroll
+            for (int t = 0; t < NT; ++t) acc[m][t] = 0.f;
+        if (c < nchunk) {
+            int k0, k1;
+            chunk_offsets<WT>(c, k0, k1);
+#pragma unroll
+            for (int t = 0; t < NT; ++t) {
+                acc[0][t] = qraw_dot<WT>(buf[b][0], xq + (size_t)t * K, xd + (size_t)t * nchunk, xs16 + (size_t)t * (K >> 4), k0, k1);
+                acc[1][t] = qraw_dot<WT>(buf[b][1], xq + (size_t)t * K, xd + (size_t)t * nchunk, xs16 + (size_t)t * (K >> 4), k0, k1);
+            }
+        }
+        float* dst = partial + ((size_t)g * KC + cu) * 2 * NT;
+#pragma unroll
+        for (int m = 0; m < 2; ++m)
+#pragma unroll
+            for (int t = 0; t < NT; ++t) {
+                const float v = warp_sum(acc[m][t]);
+                if (lane == 0) dst[m * NT + t] = v;
+            }
+    };
+
+    int u = warp;
+    if (threadIdx.x == 0) next_unit = 8;
+    if (u < n_units) issue(u, 0);              // before the dependency wait: weights are static
+    pdl_wait();
+    stage_x<NT>(p, K, xs, red);
+    // quantise the staged activations: one 32-block per 8 threads (4 values each)
+    for (int i = threadIdx.x; i < NT * (K >> 2); i += blockDim.x) {
+        const __half2* hp = reinterpret_cast<const __half2*>(xs) + (size_t)i * 2;
+        const float2 a = __half22float2(hp[0]), b = __half22float2(hp[1]);
+        float amax = fmaxf(fmaxf(fabsf(a.x), fabsf(a.y)), fmaxf(fabsf(b.x), fabsf(b.y)));
+        float s4 = a.x + a.y + b.x + b.y;
+        amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, 1));
+        amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, 2));
+        amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, 4));
+        s4 += __shfl_xor_sync(0xffffffffu, s4, 1);
+        s4 += __shfl_xor_sync(0xffffffffu, s4, 2);           // sum over 16 values (4 threads)
+        const float d = amax / 127.f, inv = amax > 0.f ? 127.f / amax : 0.f;
+        const int q0 = __float2int_rn(a.x * inv), q1 = __float2int_rn(a.y * inv), q2 = __float2int_rn(b.x * inv), q3 = __float2int_rn(b.y * inv);
+        reinterpret_cast<uint32_t*>(xq)[i] = (uint32_t)(q0 & 0xff) | ((uint32_t)(q1 & 0xff) << 8) | ((uint32_t)(q2 & 0xff) << 16) | ((uint32_t)(q3 & 0xff) << 24);
+        if ((i & 7) == 0) xd[i >> 3] = d;
+        if ((i & 3) == 0) xs16[i >> 2] = s4;
+    }
+    __syncthreads();
+
+    while (u < n_units) {
+        int un = 0;
+        if (lane == 0) un = atomicAdd(&next_unit, 1);
+        un = __shfl_sync(0xffffffffu, un, 0);
+        if (un < n_units) issue(un, 1);
+        reduce(u, 0);
+        if (un >= n_units) break;
+        int u2 = 0;
+        if (lane == 0) u2 = atomicAdd(&next_unit, 1);
+        u2 = __shfl_sync(0xffffffffu, u2, 0);
+        if (u2 < n_units) issue(u2, 0);
+        reduce(un, 1);
+        u = u2;
+    }
+    pdl_launch_dependents();
+    __syncthreads();
+    const int n_rows = (g_hi - g_lo) * rpu;
+    for (int idx = threadIdx.x; idx < n_rows * NT; idx += blockDim.x) {
+        const int rl = idx / NT, t = idx % NT;
+        const int g = rl / rpu, m = dual ? 0 : (rl % rpu);
+        const int row = (g_lo + g) * rpu + (dual ? 0 : m);
+        if (row >= N) continue;
+        float v0 = 0.f, v1 = 0.f;
+        for (int c = 0; c < KC; ++c) {
+            const float* q = partial + ((size_t)g * KC + c) * 2 * NT;
+            v0 += q[m * NT + t];
+            if (dual) v1 += q[NT + t];
+        }
+        const size_t o = (size_t)t * p.ldy + row;
+        if (p.out_mode == GV_PUSH_F32) {
+            for (int pr = 0; pr < p.ar_out.tp; ++pr) p.ar_out.peer_buf[pr][((size_t)p.ar_out.rank * NT + t) * N + row] = v0;
+        } else if (p.out_mode == GV_STORE_F16) reinterpret_cast<__half*>(p.y)[o] = __float2half_rn(v0);
+        else if (p.out_mode == GV_STORE_F32) reinterpret_cast<float*>(p.y)[o] = v0;
+        else if (p.out_mode == GV_ADD_F32) reinterpret_cast<float*>(p.y)[o] += v0;
+        else reinterpret_cast<__half*>(p.y)[o] = __float2half_rn(gv_silu(v0) * v1);
+    }
+    if (p.out_mode == GV_PUSH_F32) ar_signal(p.ar_out);
+}
+
+template <typename Kern>
+static int launch_gemv_qv3(Kern kern, const GemvParams& p, size_t x_smem, cudaStream_t stream) {
+    static thread_local const void* configured[32];
+    static thread_local int n_configured = 0;
+    bool seen = false;
+    for (int i = 0; i < n_configured; ++i) seen |= configured[i] == (const void*)kern;
+    if (!seen) {
+        DLP_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
+        if (n_configured < 32) configured[n_configured++] = (const void*)kern;
+    }
+    const bool dual = p.out_mode == GV_SWIGLU_F16;
+    const int rpu = dual ? 1 : 2;
+    const int groups = (p.w0.N + rpu - 1) / rpu;
+    int blocks = sm_count() * 2;
+    if (blocks > groups) blocks = groups;
+    const int K = p.w0.K, KC = ((K >> 5) + 31) >> 5;
+    const int max_groups = (groups + blocks - 1) / blocks + 1;
+    const size_t smem = ((x_smem + 15) & ~size_t(15)) + (size_t)p.T * (K + (K >> 5) * 4 + (K >> 4) * 4) + (size_t)max_groups * KC * 2 * p.T * sizeof(float);
+    if (smem > 100 * 1024) return -2;   // caller falls back to v1
+    DLP_CHECK_CUDA(launch_pdl(kern, dim3(blocks), dim3(256), smem, stream, p));
+    return 0;
+}
+
 // ---------------------------------------------------------------------------------------------
 template <typename Kern>
 static int launch_gemv(Kern kern, const GemvParams& p, size_t smem, cudaStream_t stream) {
@@ -693,6 +955,21 @@ int gemv(const GemvParams& p, int wtype, cudaStream_t stream) {
             if (T == 4) { if (U == 4) { DLP_V3(4, 4) } else if (U == 2) { DLP_V3(4, 2) } else { DLP_V3(4, 1) } }
         }
 #undef DLP_V3
+    }
+    static int use_qv3 = -1;
+    if (use_qv3 < 0) { const char* e = getenv("DLP_GEMV_QV3"); use_qv3 = (e && e[0] == '0') ? 0 : 1; }
+    if (use_qv3 && (wtype == W_Q8_0 || wtype == W_Q4_K || wtype == W_Q5_K || wtype == W_Q6_K)) {
+        const size_t xsm = (size_t)T * K * 2 + (p.ar_in.buf ? (size_t)K * 4 : 0);
+        int rc = -2;
+#define DLP_QV3(WT_)                                                                                       \
+    case WT_:                                                                                              \
+        rc = T == 1 ? launch_gemv_qv3(gemv_quant_v3_kernel<WT_, 1>, p, xsm, stream)                        \
+           : T == 2 ? launch_gemv_qv3(gemv_quant_v3_kernel<WT_, 2>, p, xsm, stream)                        \
+                    : launch_gemv_qv3(gemv_quant_v3_kernel<WT_, 4>, p, xsm, stream);                       \
+        break;
+        switch (wtype) { DLP_QV3(W_Q8_0) DLP_QV3(W_Q4_K) DLP_QV3(W_Q5_K) DLP_QV3(W_Q6_K) }
+#undef DLP_QV3
+        if (rc != -2) return rc;
     }
     switch (wtype) {
         case W_F16:

@@ -45,10 +45,13 @@ def test_gemv_store_and_add(t, T):
     ref = x.float() @ exact.T
     y16 = ops.linear(w, x, "f16")
     y32 = ops.linear(w, x, "f32")
-    assert nmse(ref, y32) < 5e-6 and nmse(ref, y16) < 5e-6
+    # block-quantised weights use int8 activations + dp4a on the decode path (the reference's q8_1 numerics class;
+    # its own MUL_MAT tolerance is 5e-4): allow 5e-5 there, 5e-6 for the dense types
+    tol = 5e-5 if t.name.startswith("Q") else 5e-6
+    assert nmse(ref, y32) < tol and nmse(ref, y16) < tol
     acc = torch.ones(T, N, device=DEV)
     ops.linear(w, x, "add", out=acc)
-    assert nmse(ref + 1, acc) < 5e-6
+    assert nmse(ref + 1, acc) < tol
 
 
 @pytest.mark.parametrize("t", [GGMLType.F16, GGMLType.Q8_0, GGMLType.Q4_K, GGMLType.Q6_K])
@@ -62,7 +65,7 @@ def test_gemv_fused_norm_and_swiglu(t):
     xn = (h * torch.rsqrt(h.pow(2).mean(-1, keepdim=True) + eps) * nw).half().float()
     ref = torch.nn.functional.silu(xn @ eg.T) * (xn @ eu.T)
     y = ops.linear(wg, h, "swiglu", w_up=wu, norm_w=nw, eps=eps)
-    assert nmse(ref, y) < 2e-5
+    assert nmse(ref, y) < (2e-4 if t.name.startswith("Q") else 2e-5)
 
 
 @pytest.mark.parametrize("T,N,K", [(5, 128, 64), (16, 256, 256), (37, 384, 1024), (128, 512, 512), (300, 128, 2048), (512, 1024, 4096)])
@@ -270,8 +273,8 @@ def test_fused_allreduce_protocol_virtual_ranks(t, T):
             h_out = torch.zeros_like(h)
             y = torch.empty(T, 256, device=DEV)
             c.gemv(wn, h, 1, T, out=y, norm_w=nw, eps=1e-5, ar_in=c.ar_in(0, h_out))
-            assert nmse(h_ref, h_out) < 1e-6
-            assert nmse(y_ref, y) < 2e-5
+            assert nmse(h_ref, h_out) < (1e-5 if t.name.startswith("Q") else 1e-6)
+            assert nmse(y_ref, y) < (1e-4 if t.name.startswith("Q") else 2e-5)
             c.check_error()
         act = (act.float() * 0.5 + 0.1).half()
 
