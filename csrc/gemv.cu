@@ -633,41 +633,33 @@ __global__ void __launch_bounds__(256) gemv_quant_kernel(const GemvParams p) {
 // 32-weight chunk with 8 dp4a, so all formats stream at memory speed.  Per chunk:  w_i = scale*q_i + bias  gives
 //   sum_i w_i x_i  ~=  scale * dx * dot_int(q, xq) + bias * sum_i x_i     (the last sum is kept in fp32, exact)
 // For Q6_K the stored 6-bit value is q+32: dot_int(u, xq) - 32 * sum_int(xq) recovers the signed product exactly.
+// Raw register images of one 32-weight chunk.  qraw_load() only *issues* loads (no instruction may depend on their
+// results, or the warp would stall for a full memory latency per unit); all decoding happens in qraw_dot().
 template <int WT> struct QRaw;
-template <> struct QRaw<W_Q8_0> { uint4 a, b; float d; };
-template <> struct QRaw<W_Q4_K> { uint4 qs; float s0, s1, b0, b1; };
-template <> struct QRaw<W_Q5_K> { uint4 qs, qh; float s0, s1, b0, b1; int sh; };
-template <> struct QRaw<W_Q6_K> { uint4 ql, qh; float s0, s1; int sh; };
+template <> struct QRaw<W_Q8_0> { uint4 a, b; unsigned short d; };
+template <> struct QRaw<W_Q4_K> { uint4 hdr, qs; };
+template <> struct QRaw<W_Q5_K> { uint4 hdr, qs, qh; };
+template <> struct QRaw<W_Q6_K> { uint4 ql, qh; unsigned short d; signed char s0, s1; };
 
 template <int WT> __device__ __forceinline__ void qraw_load(const QWeight& w, int row, int c, QRaw<WT>& r);
 template <> __device__ __forceinline__ void qraw_load<W_Q8_0>(const QWeight& w, int row, int c, QRaw<W_Q8_0>& r) {
     const uint8_t* qs = w.base + (size_t)row * w.K + (size_t)c * 32;
     r.a = ldg_nc_v4(qs);
     r.b = ldg_nc_v4(qs + 16);
-    r.d = __half2float(reinterpret_cast<const __half*>(w.aux0)[(size_t)row * (w.K >> 5) + c]);
+    r.d = __ldg(reinterpret_cast<const unsigned short*>(w.aux0) + (size_t)row * (w.K >> 5) + c);
 }
 template <> __device__ __forceinline__ void qraw_load<W_Q4_K>(const QWeight& w, int row, int c, QRaw<W_Q4_K>& r) {
     const int blk = c >> 3, j = (c & 7) >> 1, l0 = (c & 1) * 16;
     const uint8_t* b = w.base + ((size_t)row * (w.K >> 8) + blk) * 144;
-    const uint4 hdr = __ldg(reinterpret_cast<const uint4*>(b));
+    r.hdr = __ldg(reinterpret_cast<const uint4*>(b));
     r.qs = ldg_nc_v4(b + 16 + j * 32 + l0);
-    const float2 dm = h2_to_f2(hdr.x);
-    int sc0, mn0, sc1, mn1;
-    scale_min_k4(hdr.y, hdr.z, hdr.w, 2 * j, sc0, mn0);
-    scale_min_k4(hdr.y, hdr.z, hdr.w, 2 * j + 1, sc1, mn1);
-    r.s0 = dm.x * sc0; r.s1 = dm.x * sc1; r.b0 = -dm.y * mn0; r.b1 = -dm.y * mn1;
 }
 template <> __device__ __forceinline__ void qraw_load<W_Q5_K>(const QWeight& w, int row, int c, QRaw<W_Q5_K>& r) {
     const int blk = c >> 3, j = (c & 7) >> 1, l0 = (c & 1) * 16;
     const uint8_t* b = w.base + ((size_t)row * (w.K >> 8) + blk) * 176;
-    const uint4 hdr = __ldg(reinterpret_cast<const uint4*>(b));
+    r.hdr = __ldg(reinterpret_cast<const uint4*>(b));
     r.qh = __ldg(reinterpret_cast<const uint4*>(b + 16 + l0));
     r.qs = ldg_nc_v4(b + 48 + j * 32 + l0);
-    const float2 dm = h2_to_f2(hdr.x);
-    int sc0, mn0, sc1, mn1;
-    scale_min_k4(hdr.y, hdr.z, hdr.w, 2 * j, sc0, mn0);
-    scale_min_k4(hdr.y, hdr.z, hdr.w, 2 * j + 1, sc1, mn1);
-    r.s0 = dm.x * sc0; r.s1 = dm.x * sc1; r.b0 = -dm.y * mn0; r.b1 = -dm.y * mn1; r.sh = 2 * j;
 }
 template <> __device__ __forceinline__ void qraw_load<W_Q6_K>(const QWeight& w, int row, int c, QRaw<W_Q6_K>& r) {
     const int blk = c >> 3, cc = c & 7, half = cc >> 2, l0 = (cc & 3) * 16;
@@ -675,9 +667,10 @@ template <> __device__ __forceinline__ void qraw_load<W_Q6_K>(const QWeight& w, 
     const size_t nblk = (size_t)row * (w.K >> 8) + blk;
     r.ql = ldg_nc_v4(w.base + nblk * 128 + half * 64 + l0);
     r.qh = ldg_nc_v4(w.aux0 + nblk * 64 + half * 32 + lq);
-    const int8_t* sc = reinterpret_cast<const int8_t*>(w.aux1) + nblk * 16 + half * 8 + (lq >> 4) + upper * 2;
-    const float d = __half2float(reinterpret_cast<const __half*>(w.aux2)[nblk]);
-    r.s0 = d * (float)sc[0]; r.s1 = d * (float)sc[4]; r.sh = upper * 2;
+    const signed char* sc = reinterpret_cast<const signed char*>(w.aux1) + nblk * 16 + half * 8 + (lq >> 4) + upper * 2;
+    r.s0 = __ldg(sc);
+    r.s1 = __ldg(sc + 4);
+    r.d = __ldg(reinterpret_cast<const unsigned short*>(w.aux2) + nblk);
 }
 
 // element offsets of the two 16-element groups of chunk c (same mapping as load_chunk in quant.cuh)
@@ -696,16 +689,27 @@ __device__ __forceinline__ int dp4a4(const uint32_t (&q)[4], const uint4& x) {
     return __dp4a((int)q[3], (int)x.w, s);
 }
 
-// dot of one raw chunk with token t's int8 activations; xq int8 [K], xd fp32 [K/32] scales, xs16 fp32 [K/16] exact sums
+__device__ __forceinline__ float us2f(unsigned short h) { return __half2float(__ushort_as_half(h)); }
+
+// dot of one raw chunk with token t's int8 activations; xq int8 [K], xd fp32 [K/32] scales, xs16 fp32 [K/16] exact sums.
+// `c` is the chunk index (needed to pick the sub-block scales).  Unsigned quant values are centred before the integer dot
+// ( sum (q-z) xq = dp4a(q, xq) - z * dp4a(1, xq) ), which keeps the activation-rounding noise off the large offset term.
 template <int WT>
-__device__ __forceinline__ float qraw_dot(const QRaw<WT>& r, const int8_t* xq, const float* xd, const float* xs16, int k0, int k1) {
+__device__ __forceinline__ float qraw_dot(const QRaw<WT>& r, const int8_t* xq, const float* xd, const float* xs16, int c, int k0, int k1) {
     const uint4 xa = *reinterpret_cast<const uint4*>(xq + k0);
     const uint4 xb = *reinterpret_cast<const uint4*>(xq + k1);
+    const uint32_t ones[4] = {0x01010101u, 0x01010101u, 0x01010101u, 0x01010101u};
     if constexpr (WT == W_Q8_0) {
         const uint32_t qa[4] = {r.a.x, r.a.y, r.a.z, r.a.w}, qb[4] = {r.b.x, r.b.y, r.b.z, r.b.w};
         const int isum = dp4a4(qa, xa) + dp4a4(qb, xb);
-        return r.d * xd[k0 >> 5] * (float)isum;
+        return us2f(r.d) * xd[k0 >> 5] * (float)isum;
     } else if constexpr (WT == W_Q4_K || WT == W_Q5_K) {
+        const int j = (c & 7) >> 1;
+        const float2 dm = h2_to_f2(r.hdr.x);
+        int sc0, mn0, sc1, mn1;
+        scale_min_k4(r.hdr.y, r.hdr.z, r.hdr.w, 2 * j, sc0, mn0);
+        scale_min_k4(r.hdr.y, r.hdr.z, r.hdr.w, 2 * j + 1, sc1, mn1);
+        const float s0 = dm.x * sc0, s1 = dm.x * sc1;
         const uint32_t w4[4] = {r.qs.x, r.qs.y, r.qs.z, r.qs.w};
         uint32_t lo[4], hi[4];
 #pragma unroll
@@ -713,29 +717,32 @@ __device__ __forceinline__ float qraw_dot(const QRaw<WT>& r, const int8_t* xq, c
             lo[i] = w4[i] & 0x0F0F0F0Fu;
             hi[i] = (w4[i] >> 4) & 0x0F0F0F0Fu;
         }
+        constexpr int Z = (WT == W_Q5_K) ? 16 : 8;
         if constexpr (WT == W_Q5_K) {
             const uint32_t h4[4] = {r.qh.x, r.qh.y, r.qh.z, r.qh.w};
 #pragma unroll
             for (int i = 0; i < 4; ++i) {
-                lo[i] |= ((h4[i] >> r.sh) & 0x01010101u) << 4;
-                hi[i] |= ((h4[i] >> (r.sh + 1)) & 0x01010101u) << 4;
+                lo[i] |= ((h4[i] >> (2 * j)) & 0x01010101u) << 4;
+                hi[i] |= ((h4[i] >> (2 * j + 1)) & 0x01010101u) << 4;
             }
         }
-        const float d0 = r.s0 * xd[k0 >> 5] * (float)dp4a4(lo, xa);
-        const float d1 = r.s1 * xd[k1 >> 5] * (float)dp4a4(hi, xb);
-        return d0 + d1 + r.b0 * xs16[k0 >> 4] + r.b1 * xs16[k1 >> 4];
-    } else {   // Q6_K
+        const int ia = dp4a4(lo, xa) - Z * dp4a4(ones, xa);
+        const int ib = dp4a4(hi, xb) - Z * dp4a4(ones, xb);
+        const float b0 = (float)Z * s0 - dm.y * mn0, b1 = (float)Z * s1 - dm.y * mn1;
+        return s0 * xd[k0 >> 5] * (float)ia + s1 * xd[k1 >> 5] * (float)ib + b0 * xs16[k0 >> 4] + b1 * xs16[k1 >> 4];
+    } else {   // Q6_K: stored value = q + 32
+        const int sh = (((c & 7) & 3) * 16 >> 5) * 2;
         const uint32_t l4[4] = {r.ql.x, r.ql.y, r.ql.z, r.ql.w}, h4[4] = {r.qh.x, r.qh.y, r.qh.z, r.qh.w};
         uint32_t lo[4], hi[4];
-        const uint32_t ones[4] = {0x01010101u, 0x01010101u, 0x01010101u, 0x01010101u};
 #pragma unroll
         for (int i = 0; i < 4; ++i) {
-            lo[i] = (l4[i] & 0x0F0F0F0Fu) | (((h4[i] >> r.sh) & 0x03030303u) << 4);
-            hi[i] = ((l4[i] >> 4) & 0x0F0F0F0Fu) | (((h4[i] >> (r.sh + 4)) & 0x03030303u) << 4);
+            lo[i] = (l4[i] & 0x0F0F0F0Fu) | (((h4[i] >> sh) & 0x03030303u) << 4);
+            hi[i] = ((l4[i] >> 4) & 0x0F0F0F0Fu) | (((h4[i] >> (sh + 4)) & 0x03030303u) << 4);
         }
         const int ia = dp4a4(lo, xa) - 32 * dp4a4(ones, xa);
         const int ib = dp4a4(hi, xb) - 32 * dp4a4(ones, xb);
-        return r.s0 * xd[k0 >> 5] * (float)ia + r.s1 * xd[k1 >> 5] * (float)ib;
+        const float d = us2f(r.d);
+        return d * (float)r.s0 * xd[k0 >> 5] * (float)ia + d * (float)r.s1 * xd[k1 >> 5] * (float)ib;
     }
 }
 
@@ -787,8 +794,8 @@ __global__ void __launch_bounds__(256, 2) gemv_quant_v3_kernel(const GemvParams 
             chunk_offsets<WT>(c, k0, k1);
 #pragma unroll
             for (int t = 0; t < NT; ++t) {
-                acc[0][t] = qraw_dot<WT>(buf[b][0], xq + (size_t)t * K, xd + (size_t)t * nchunk, xs16 + (size_t)t * (K >> 4), k0, k1);
-                acc[1][t] = qraw_dot<WT>(buf[b][1], xq + (size_t)t * K, xd + (size_t)t * nchunk, xs16 + (size_t)t * (K >> 4), k0, k1);
+                acc[0][t] = qraw_dot<WT>(buf[b][0], xq + (size_t)t * K, xd + (size_t)t * nchunk, xs16 + (size_t)t * (K >> 4), c, k0, k1);
+                acc[1][t] = qraw_dot<WT>(buf[b][1], xq + (size_t)t * K, xd + (size_t)t * nchunk, xs16 + (size_t)t * (K >> 4), c, k0, k1);
             }
         }
         float* dst = partial + ((size_t)g * KC + cu) * 2 * NT;

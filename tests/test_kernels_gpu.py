@@ -273,8 +273,8 @@ def test_fused_allreduce_protocol_virtual_ranks(t, T):
             h_out = torch.zeros_like(h)
             y = torch.empty(T, 256, device=DEV)
             c.gemv(wn, h, 1, T, out=y, norm_w=nw, eps=1e-5, ar_in=c.ar_in(0, h_out))
-            assert nmse(h_ref, h_out) < (1e-5 if t.name.startswith("Q") else 1e-6)
-            assert nmse(y_ref, y) < (1e-4 if t.name.startswith("Q") else 2e-5)
+            assert nmse(h_ref, h_out) < (1e-4 if t.name.startswith("Q") else 1e-6)
+            assert nmse(y_ref, y) < (3e-4 if t.name.startswith("Q") else 2e-5)
             c.check_error()
         act = (act.float() * 0.5 + 0.1).half()
 
