@@ -773,7 +773,8 @@ __global__ void __launch_bounds__(256, 2) gemv_quant_v3_kernel(const GemvParams 
     const int g_hi = (int)(((long long)groups_total * (blockIdx.x + 1)) / gridDim.x);
     const int n_units = (g_hi - g_lo) * KC;
 
-    QRaw<WT> buf[2][2];   // [double buffer][row stream]
+    constexpr int DEPTH = sizeof(QRaw<WT>) >= 36 ? 3 : 4;   // units in flight per warp (ncu: two were not enough to cover HBM latency, 1.5-3.3 TB/s)
+    QRaw<WT> buf[DEPTH][2];   // [ring slot][row stream]
     auto issue = [&](int u, int b) {
         const int g = g_lo + u / KC, c = (u % KC) * 32 + lane;
         if (c >= nchunk) return;
@@ -808,9 +809,13 @@ __global__ void __launch_bounds__(256, 2) gemv_quant_v3_kernel(const GemvParams 
             }
     };
 
-    int u = warp;
-    if (threadIdx.x == 0) next_unit = 8;
-    if (u < n_units) issue(u, 0);              // before the dependency wait: weights are static
+    int uu[DEPTH];
+#pragma unroll
+    for (int d = 0; d < DEPTH; ++d) {          // the first DEPTH rounds are assigned statically so they can start right now,
+        uu[d] = warp + 8 * d;                  // before the dependency wait: weights are static
+        if (uu[d] < n_units) issue(uu[d], d);
+    }
+    if (threadIdx.x == 0) next_unit = 8 * DEPTH;
     pdl_wait();
     stage_x<NT>(p, K, xs, red);
     // quantise the staged activations: one 32-block per 8 threads (4 values each)
@@ -832,19 +837,21 @@ __global__ void __launch_bounds__(256, 2) gemv_quant_v3_kernel(const GemvParams 
     }
     __syncthreads();
 
-    while (u < n_units) {
-        int un = 0;
-        if (lane == 0) un = atomicAdd(&next_unit, 1);
-        un = __shfl_sync(0xffffffffu, un, 0);
-        if (un < n_units) issue(un, 1);
-        reduce(u, 0);
-        if (un >= n_units) break;
-        int u2 = 0;
-        if (lane == 0) u2 = atomicAdd(&next_unit, 1);
-        u2 = __shfl_sync(0xffffffffu, u2, 0);
-        if (u2 < n_units) issue(u2, 0);
-        reduce(un, 1);
-        u = u2;
+    for (;;) {                                 // ring of DEPTH prefetched units per warp, refilled from the shared counter
+        bool did = false;
+#pragma unroll
+        for (int d = 0; d < DEPTH; ++d) {
+            if (uu[d] < n_units) {
+                reduce(uu[d], d);
+                int un = 0;
+                if (lane == 0) un = atomicAdd(&next_unit, 1);
+                un = __shfl_sync(0xffffffffu, un, 0);
+                uu[d] = un;
+                if (un < n_units) issue(un, d);
+                did = true;
+            }
+        }
+        if (!did) break;
     }
     pdl_launch_dependents();
     __syncthreads();
