@@ -41,12 +41,15 @@ def test_two_worker_pipeline_matches_oracle(chain):
     prompt = [1, 5, 9, 200, 33, 7, 8, 100, 42]
     toks, ref_logits = ref.generate_greedy(prompt, 4)
     sid = eng.alloc_seq()
-    assert nmse(ref_logits[0], eng.prefill(sid, prompt)) < 1e-6
+    # Q8_0 runs on the int8 x int8 AVX2 path (activations quantised per 32 values, like the reference's CPU vec-dot):
+    # its own MUL_MAT tolerance is NMSE 5e-4; the fp32-decode path of the other types is exact to 1e-6
+    tol = 3e-4 if "Q8_0" in path else 1e-6
+    assert nmse(ref_logits[0], eng.prefill(sid, prompt)) < tol
     for i, t in enumerate(toks[:-1]):
-        assert nmse(ref_logits[i + 1], eng.decode([sid], [t], sample=False)[0]) < 1e-6
+        assert nmse(ref_logits[i + 1], eng.decode([sid], [t], sample=False)[0]) < tol
     # truncate = prefix reuse: rewind to the prompt and replay one step
     eng.truncate_seq(sid, len(prompt))
-    assert nmse(ref_logits[1], eng.decode([sid], [toks[0]], sample=False)[0]) < 1e-6
+    assert nmse(ref_logits[1], eng.decode([sid], [toks[0]], sample=False)[0]) < tol
     eng.free_seq(sid)
     assert [w.l0 for w in eng.workers] == [0, 1] and eng.workers[0].first and eng.workers[1].last
 

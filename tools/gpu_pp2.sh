@@ -1,0 +1,11 @@
+#!/usr/bin/env bash
+mkdir -p gpurun_out
+timeout 200 python -m pytest tests/test_parallel_gpu.py -q -k "pp2_gpu" --timeout 180 -p no:cacheprovider 2>&1 | tail -2
+python - <<'PY'
+import sys; sys.path.insert(0,'.')
+from bench import ensure_model
+print(ensure_model('llama-3-8b','Q8_0',0,lambda:None))
+PY
+M=/tmp/dlp_models/llama-3-8b-Q8_0.gguf
+timeout 300 python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 --master-port 29821 tools/dlp_bench.py -m $M --pp 2 --tp 1 -p 512 -n 128 -r 3 -o json > gpurun_out/pp2_ours.json 2> gpurun_out/pp2_ours.err; echo "ours rc=$?"; grep -E '"test"|"avg_ts"' gpurun_out/pp2_ours.json
+LD_LIBRARY_PATH=baseline/_ref/bin CUDA_VISIBLE_DEVICES=0,1 timeout 300 baseline/_ref/bin/llama-bench -m $M -ngl 99 -fa 1 -sm layer -p 512 -n 128 -r 3 -o json > gpurun_out/pp2_ref.json 2> gpurun_out/pp2_ref.err; echo "ref rc=$?"; grep -E '"n_prompt"|"n_gen"|"avg_ts"' gpurun_out/pp2_ref.json
