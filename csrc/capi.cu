@@ -100,6 +100,25 @@ int dlp_gemv_tp(const dlp_weight* w0, const dlp_weight* w1, const void* x, const
     return gemv(p, w0->wtype, (cudaStream_t)stream);
 }
 
+int dlp_gemv_moe(const dlp_weight* w0, const dlp_weight* w1, const void* x, const float* norm_w, float eps, void* y, int ldy,
+                 int out_mode, const int32_t* expert_id_dev, int rows_per_expert, const float* out_scale_dev, void* stream) {
+    DLP_REQUIRE(w0 && w0->base && x && y && expert_id_dev && rows_per_expert > 0, "dlp_gemv_moe: bad argument");
+    GemvParams p;
+    memset(&p, 0, sizeof(p));
+    p.w0 = to_qw(w0);
+    if (w1) p.w1 = to_qw(w1);
+    p.w0.N = rows_per_expert;              // the kernel walks one expert's rows; the offset selects which
+    if (w1) p.w1.N = rows_per_expert;
+    p.x = x; p.norm_w = norm_w; p.eps = eps; p.y = y; p.ldy = ldy; p.out_mode = out_mode; p.T = 1;
+    p.row_off_dev = expert_id_dev; p.row_off_mul = rows_per_expert; p.out_scale_dev = out_scale_dev;
+    return gemv(p, w0->wtype, (cudaStream_t)stream);
+}
+
+int dlp_moe_route(const float* logits, int T, int n_expert, int top_k, int32_t* ids, float* weights, void* stream) {
+    DLP_REQUIRE(logits && ids && weights && T > 0, "dlp_moe_route: bad argument");
+    return moe_route(logits, T, n_expert, top_k, ids, weights, (cudaStream_t)stream);
+}
+
 int dlp_ar_consume(const float* h_in, float* h_out, const dlp_ar_in* ar_in, int E, int T, void* stream) {
     DLP_REQUIRE(h_in && h_out && ar_in && ar_in->buf, "dlp_ar_consume: null argument");
     ArIn a;

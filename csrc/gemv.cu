@@ -249,12 +249,13 @@ __global__ void __launch_bounds__(256, 2) gemv_dense_v3_kernel(const GemvParams 
     const int n_units = (g_hi - g_lo) * KC;
 
     uint4 buf[2][2][U];   // [double buffer][stream][load]
+    int roff = 0;         // expert row offset (MoE), known only after the router kernel has finished
     auto issue = [&](int u, int b) {
         const int g = g_lo + u / KC, c = u % KC;
         const int row = g * rpu;
-        const uint8_t* s0 = p.w0.base + ((size_t)row * K + (size_t)c * KCW + lane * 8) * 2;
-        const uint8_t* s1 = dual ? p.w1.base + ((size_t)row * K + (size_t)c * KCW + lane * 8) * 2
-                                 : p.w0.base + ((size_t)min(row + 1, N - 1) * K + (size_t)c * KCW + lane * 8) * 2;
+        const uint8_t* s0 = p.w0.base + ((size_t)(row + roff) * K + (size_t)c * KCW + lane * 8) * 2;
+        const uint8_t* s1 = dual ? p.w1.base + ((size_t)(row + roff) * K + (size_t)c * KCW + lane * 8) * 2
+                                 : p.w0.base + ((size_t)(min(row + 1, N - 1) + roff) * K + (size_t)c * KCW + lane * 8) * 2;
 #pragma unroll
         for (int i = 0; i < U; ++i) {
             buf[b][0][i] = ldg_nc_v4(s0 + (size_t)i * 512);
@@ -304,8 +305,14 @@ __global__ void __launch_bounds__(256, 2) gemv_dense_v3_kernel(const GemvParams 
 
     int u = warp;                              // the first round is assigned statically so that it can start right now
     if (threadIdx.x == 0) next_unit = 8;
-    if (u < n_units) issue(u, 0);              // weights are static: requested before the predecessor has finished
+    const bool dyn_rows = p.row_off_dev != nullptr;
+    if (!dyn_rows && u < n_units) issue(u, 0); // weights are static: requested before the predecessor has finished
     pdl_wait();
+    if (dyn_rows) {
+        roff = (*p.row_off_dev) * p.row_off_mul;
+        if (u < n_units) issue(u, 0);
+    }
+    const float oscale = p.out_scale_dev ? *p.out_scale_dev : 1.f;
     stage_x<NT>(p, K, xs, red);                // (ends with __syncthreads: next_unit is visible)
 
     while (u < n_units) {                      // software pipeline, unrolled by two for static register indexing
@@ -337,6 +344,7 @@ __global__ void __launch_bounds__(256, 2) gemv_dense_v3_kernel(const GemvParams 
             v0 += q[m * NT + t];
             if (dual) v1 += q[NT + t];
         }
+        if (!dual) v0 *= oscale;
         const size_t o = (size_t)t * p.ldy + row;
         if (p.out_mode == GV_PUSH_F32) {
             for (int pr = 0; pr < p.ar_out.tp; ++pr) p.ar_out.peer_buf[pr][((size_t)p.ar_out.rank * NT + t) * N + row] = v0;
@@ -775,13 +783,14 @@ __global__ void __launch_bounds__(256, 2) gemv_quant_v3_kernel(const GemvParams 
 
     constexpr int DEPTH = sizeof(QRaw<WT>) >= 36 ? 3 : 4;   // units in flight per warp (ncu: two were not enough to cover HBM latency, 1.5-3.3 TB/s)
     QRaw<WT> buf[DEPTH][2];   // [ring slot][row stream]
+    int roff = 0;             // expert row offset (MoE)
     auto issue = [&](int u, int b) {
         const int g = g_lo + u / KC, c = (u % KC) * 32 + lane;
         if (c >= nchunk) return;
         const int row = g * rpu;
-        qraw_load<WT>(p.w0, row, c, buf[b][0]);
-        if (dual) qraw_load<WT>(p.w1, row, c, buf[b][1]);
-        else qraw_load<WT>(p.w0, min(row + 1, N - 1), c, buf[b][1]);
+        qraw_load<WT>(p.w0, row + roff, c, buf[b][0]);
+        if (dual) qraw_load<WT>(p.w1, row + roff, c, buf[b][1]);
+        else qraw_load<WT>(p.w0, min(row + 1, N - 1) + roff, c, buf[b][1]);
     };
     auto reduce = [&](int u, int b) {
         const int g = u / KC, cu = u % KC, c = cu * 32 + lane;
@@ -810,13 +819,21 @@ __global__ void __launch_bounds__(256, 2) gemv_quant_v3_kernel(const GemvParams 
     };
 
     int uu[DEPTH];
+    const bool dyn_rows = p.row_off_dev != nullptr;
 #pragma unroll
     for (int d = 0; d < DEPTH; ++d) {          // the first DEPTH rounds are assigned statically so they can start right now,
         uu[d] = warp + 8 * d;                  // before the dependency wait: weights are static
-        if (uu[d] < n_units) issue(uu[d], d);
+        if (!dyn_rows && uu[d] < n_units) issue(uu[d], d);
     }
     if (threadIdx.x == 0) next_unit = 8 * DEPTH;
     pdl_wait();
+    if (dyn_rows) {
+        roff = (*p.row_off_dev) * p.row_off_mul;
+#pragma unroll
+        for (int d = 0; d < DEPTH; ++d)
+            if (uu[d] < n_units) issue(uu[d], d);
+    }
+    const float oscale = p.out_scale_dev ? *p.out_scale_dev : 1.f;
     stage_x<NT>(p, K, xs, red);
     // quantise the staged activations: one 32-block per 8 threads (4 values each)
     for (int i = threadIdx.x; i < NT * (K >> 2); i += blockDim.x) {
@@ -867,6 +884,7 @@ __global__ void __launch_bounds__(256, 2) gemv_quant_v3_kernel(const GemvParams 
             v0 += q[m * NT + t];
             if (dual) v1 += q[NT + t];
         }
+        if (!dual) v0 *= oscale;
         const size_t o = (size_t)t * p.ldy + row;
         if (p.out_mode == GV_PUSH_F32) {
             for (int pr = 0; pr < p.ar_out.tp; ++pr) p.ar_out.peer_buf[pr][((size_t)p.ar_out.rank * NT + t) * N + row] = v0;
@@ -898,6 +916,42 @@ static int launch_gemv_qv3(Kern kern, const GemvParams& p, size_t x_smem, cudaSt
     const size_t smem = ((x_smem + 15) & ~size_t(15)) + (size_t)p.T * (K + (K >> 5) * 4 + (K >> 4) * 4) + (size_t)max_groups * KC * 2 * p.T * sizeof(float);
     if (smem > 100 * 1024) return -2;   // caller falls back to v1
     DLP_CHECK_CUDA(launch_pdl(kern, dim3(blocks), dim3(256), smem, stream, p));
+    return 0;
+}
+
+// ---- MoE router: softmax over all experts -> top-k -> renormalise (llama-graph.cpp:1039-1139; topk-moe.cu) ---------------
+__global__ void moe_route_kernel(const float* __restrict__ logits, int n_expert, int top_k, int* __restrict__ ids, float* __restrict__ w) {
+    pdl_wait();
+    pdl_launch_dependents();
+    const int t = blockIdx.x, lane = threadIdx.x;
+    float v = lane < n_expert ? logits[(size_t)t * n_expert + lane] : -INFINITY;
+    const float mx = warp_max(v);
+    float pr = lane < n_expert ? __expf(v - mx) : 0.f;
+    const float sum = warp_sum(pr);
+    pr /= sum;
+    float wsum = 0.f, mine_w = 0.f;
+    int mine_slot = -1;
+    for (int j = 0; j < top_k; ++j) {          // iterative arg-max, ties to the lower expert index
+        float best = pr;
+        int bi = lane;
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            const float ov = __shfl_xor_sync(0xffffffffu, best, o);
+            const int oi = __shfl_xor_sync(0xffffffffu, bi, o);
+            if (ov > best || (ov == best && oi < bi)) { best = ov; bi = oi; }
+        }
+        if (lane == bi) { mine_slot = j; mine_w = pr; pr = -1.f; }
+        wsum += best;
+    }
+    if (mine_slot >= 0) {
+        ids[t * top_k + mine_slot] = lane;
+        w[t * top_k + mine_slot] = mine_w / wsum;
+    }
+}
+
+int moe_route(const float* logits, int T, int n_expert, int top_k, int* ids, float* w, cudaStream_t s) {
+    DLP_REQUIRE(n_expert >= 1 && n_expert <= 32 && top_k >= 1 && top_k <= n_expert, "moe_route: n_expert must be <= 32 (got %d)", n_expert);
+    DLP_CHECK_CUDA(launch_pdl(moe_route_kernel, dim3(T), dim3(32), 0, s, logits, n_expert, top_k, ids, w));
     return 0;
 }
 
@@ -954,6 +1008,7 @@ int gemv(const GemvParams& p, int wtype, cudaStream_t stream) {
             }
         }
     }
+    DLP_REQUIRE(p.row_off_dev == nullptr || (T == 1 && K % 256 == 0), "gemv: expert-indexed weights need T == 1");
     static int use_v3 = -1;
     if (use_v3 < 0) { const char* e = getenv("DLP_GEMV_V3"); use_v3 = (e && e[0] == '0') ? 0 : 1; }
     if (use_v3 && (wtype == W_F16 || wtype == W_BF16)) {

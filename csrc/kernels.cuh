@@ -34,7 +34,13 @@ struct GemvParams {
     int T;
     ArIn ar_in;
     ArOut ar_out;
+    // expert-indexed weights (MoE decode): weight row = row + (*row_off_dev) * row_off_mul, outputs scaled by *out_scale_dev.
+    // Both values are produced on the device by the router, so the step stays graph-capturable.
+    const int* row_off_dev;
+    int row_off_mul;
+    const float* out_scale_dev;
 };
+int moe_route(const float* logits, int T, int n_expert, int top_k, int* ids, float* w, cudaStream_t s);
 
 // Collectives fused into the tcgen05 GEMM (prefill / batched decode under tensor parallelism, sequence-parallel layout):
 //   X side ("all-gather -> GEMM"): token rows [src*x_rows_per_src, +x_rows_per_src) of X were pushed by rank src into this

@@ -256,6 +256,9 @@ class LlamaEngine:
         Round-1 implementation: router + expert selection on the host side of the stream (not graph-capturable)."""
         cfg, comm = self.cfg, self.comm
         h = self.h[:T]
+        if (T <= 4 and lw.e_gate_s is not None and cfg.n_expert <= 32 and cfg.n_embd % 256 == 0 and comm.tp_size == 1
+                and lw.router_w.N % 2 == 0):
+            return self._moe_device(lw, T)
         if xn is None:
             xn = ops.rmsnorm(h, lw.ffn_norm, cfg.rms_eps, out=self.xn[:T])
         logits = xn.float() @ lw.router.T
@@ -274,6 +277,32 @@ class LlamaEngine:
         if comm.tp_size > 1:
             out = comm.allreduce_delta(out, -1, 1)
         h.add_(out)
+
+    def _moe_device(self, lw, T: int):
+        """Decode-path MoE entirely on the device (graph-capturable): fused-norm router mat-vec -> dlp_moe_route ->
+        per selected expert a fused-norm gate/up+SwiGLU mat-vec and a weighted down mat-vec accumulating into h."""
+        cfg = self.cfg
+        k, F = cfg.n_expert_used, self.F
+        if not hasattr(self, "moe_buf"):
+            dev = self.device
+            self.moe_buf = dict(logits=torch.zeros(4, cfg.n_expert, dtype=torch.float32, device=dev),
+                                ids=torch.zeros(4 * k, dtype=torch.int32, device=dev),
+                                w=torch.zeros(4 * k, dtype=torch.float32, device=dev),
+                                act=torch.zeros(4 * k, F, dtype=torch.float16, device=dev))
+        b = self.moe_buf
+        h = self.h[:T]
+        for t in range(T):   # router per token (T <= 4): the mat-vec path supports T in {1,2,4}, the router is tiny
+            ops.linear(lw.router_w, h[t:t + 1], "f32", norm_w=lw.ffn_norm, eps=cfg.rms_eps, out=b["logits"][t:t + 1])
+        ops.moe_route(b["logits"][:T], k, b["ids"][:T * k], b["w"][:T * k])
+        for t in range(T):
+            for j in range(k):
+                job = t * k + j
+                ops.gemv_moe(lw.e_gate_s, h[t:t + 1], b["act"][job:job + 1], "swiglu", b["ids"][job:job + 1], F, w_up=lw.e_up_s,
+                             norm_w=lw.ffn_norm, eps=cfg.rms_eps)
+            for j in range(k):   # all gate/up mat-vecs read h[t] before any down mat-vec updates it
+                job = t * k + j
+                ops.gemv_moe(lw.e_down_s, b["act"][job:job + 1], h[t:t + 1], "add", b["ids"][job:job + 1], self.E,
+                             out_scale=b["w"][job:job + 1])
 
     # ---- attention flavours ---------------------------------------------------------------------
     def _attn_decode(self, il, q, T):
@@ -457,7 +486,9 @@ class LlamaEngine:
             self.next_tok[:B].copy_(torch.as_tensor(tokens, dtype=torch.int32), non_blocking=True)
         if hidden_in is not None:
             self.h[:B].copy_(hidden_in)
-        graphable = (use_graph and self.device.type == "cuda" and not self.cfg.is_moe
+        moe_host = self.cfg.is_moe and not (B <= 4 and self.comm.tp_size == 1 and self.cfg.n_expert <= 32 and
+                                            next(iter(self.w.layers.values())).e_gate_s is not None)
+        graphable = (use_graph and self.device.type == "cuda" and not moe_host
                      and not getattr(self.comm, "no_graph", False)
                      and not (self.fused_tp and B > 4))   # SP path passes host-side epochs as kernel arguments
         if graphable:

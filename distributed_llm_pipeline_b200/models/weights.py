@@ -34,6 +34,11 @@ class LayerWeights:
     e_gate: list[DeviceWeight] = field(default_factory=list)
     e_up: list[DeviceWeight] = field(default_factory=list)
     e_down: list[DeviceWeight] = field(default_factory=list)
+    # stacked [n_expert * rows, K] views of the same memory + fp16 router (device-side MoE decode)
+    e_gate_s: DeviceWeight | None = None
+    e_up_s: DeviceWeight | None = None
+    e_down_s: DeviceWeight | None = None
+    router_w: DeviceWeight | None = None
 
 
 @dataclass
@@ -132,6 +137,17 @@ def load_weights(src: str | GGUFModelFiles, device, layer_range: range | None = 
                 lw.e_gate.append(mat(p + "ffn_gate_exps.weight", rows=(f0, f1), sub=e))
                 lw.e_up.append(mat(p + "ffn_up_exps.weight", rows=(f0, f1), sub=e))
                 lw.e_down.append(mat(p + "ffn_down_exps.weight", cols=(f0, f1), sub=e))
+            if dev.type == "cuda" and all(w.wtype == lw.e_gate[0].wtype for w in lw.e_gate + lw.e_up) and \
+                    all(w.wtype == lw.e_down[0].wtype for w in lw.e_down):
+                def restack(ws):
+                    st = stack_rows(ws)
+                    n = ws[0].N
+                    views = [DeviceWeight(st.wtype, n, st.K, [pl[e * n:(e + 1) * n] for pl in st.planes]) for e in range(len(ws))]
+                    return st, views
+                lw.e_gate_s, lw.e_gate = restack(lw.e_gate)
+                lw.e_up_s, lw.e_up = restack(lw.e_up)
+                lw.e_down_s, lw.e_down = restack(lw.e_down)
+                lw.router_w = DeviceWeight(GGMLType.F16, cfg.n_expert, cfg.n_embd, [lw.router.to(torch.float16).contiguous()])
         else:
             lw.w_gate = mat(p + "ffn_gate.weight", rows=(f0, f1))
             lw.w_up = mat(p + "ffn_up.weight", rows=(f0, f1))

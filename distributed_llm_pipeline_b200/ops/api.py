@@ -306,3 +306,32 @@ def sample(logits: torch.Tensor, top_k: int = 40, top_p: float = 0.95, min_p: fl
                                       _p(step_ctr), out.data_ptr(), _stream()), "sample")
     _count()
     return out
+
+
+# ------------------------------------------------------------------------------------------------
+def moe_route(logits: torch.Tensor, top_k: int, ids: torch.Tensor | None = None, weights: torch.Tensor | None = None):
+    """softmax over all experts -> top-k -> renormalise; returns (ids int32 [T*k], weights fp32 [T*k]) on the device."""
+    T, nE = logits.shape
+    if ids is None:
+        ids = torch.empty(T * top_k, dtype=torch.int32, device=logits.device)
+        weights = torch.empty(T * top_k, dtype=torch.float32, device=logits.device)
+    if not native(logits):
+        pr = torch.softmax(logits.float(), -1)
+        w, i = pr.topk(top_k, -1)
+        ids.copy_(i.reshape(-1).to(torch.int32))
+        weights.copy_((w / w.sum(-1, keepdim=True)).reshape(-1))
+        return ids, weights
+    _lib.check(_lib.load().dlp_moe_route(logits.data_ptr(), T, nE, top_k, ids.data_ptr(), weights.data_ptr(), _stream()), "moe_route")
+    _count()
+    return ids, weights
+
+
+def gemv_moe(w: DeviceWeight, x: torch.Tensor, out: torch.Tensor, out_mode: str, expert_id: torch.Tensor, rows_per_expert: int,
+             w_up: DeviceWeight | None = None, norm_w: torch.Tensor | None = None, eps: float = 0.0,
+             out_scale: torch.Tensor | None = None) -> torch.Tensor:
+    """One token's mat-vec against expert `expert_id[0]` (device scalar) of a stacked [n_expert*rows, K] weight."""
+    _lib.check(_lib.load().dlp_gemv_moe(w.ref(), w_up.ref() if w_up is not None else None, x.data_ptr(), _p(norm_w), eps,
+                                        out.data_ptr(), out.stride(0), _OUT[out_mode], expert_id.data_ptr(), rows_per_expert,
+                                        _p(out_scale), _stream()), "gemv_moe")
+    _count()
+    return out

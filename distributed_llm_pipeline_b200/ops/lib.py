@@ -59,6 +59,8 @@ def _declare(lib):
         "dlp_argmax": (i32, [vp, i32, i32, i32, vp, vp]),
         "dlp_sample": (i32, [vp, i32, i32, i32, i32, f32, f32, f32, u32, vp, vp, vp]),
         "dlp_f32_to_f16": (i32, [vp, vp, sz, vp]),
+        "dlp_moe_route": (i32, [vp, i32, i32, i32, vp, vp, vp]),
+        "dlp_gemv_moe": (i32, [W, W, vp, vp, f32, vp, i32, i32, vp, i32, vp, vp]),
     }
     for name, (res, args) in sigs.items():
         fn = getattr(lib, name, None)

@@ -75,10 +75,14 @@ class PipelineStage:
 
     # ---- decode: one token for each micro-batch (group of sequences) -------------------------------------
     @torch.no_grad()
-    def decode_round(self, groups: list[list[int]], tokens: list | None = None, sample: bool = True):
+    def decode_round(self, groups: list[list[int]], tokens: list | None = None, sample: bool = True, feedback: bool | None = None):
         """One decode step for every group.  `tokens[i]` (host ids) feeds group i on the first stage; when None the
-        first stage receives the ids sampled by the last stage in the previous round.  Returns, on the last stage,
-        a list of per-group results (token ids if sample else logits); elsewhere a list of None."""
+        first stage receives the ids the last stage sampled in the previous round - which must have been run with
+        `feedback=True` (default: feedback exactly when no tokens are given; pass feedback=True on a round that is
+        seeded with host tokens but followed by self-feeding rounds).  Returns, on the last stage, a list of per-group
+        results (token ids if sample else logits); elsewhere a list of None."""
+        if feedback is None:
+            feedback = tokens is None
         eng = self.eng
         nslots = len(self.rx)
         assert len(groups) <= nslots, "more micro-batches than p2p slots"
@@ -104,7 +108,7 @@ class PipelineStage:
             else:
                 res = out.clone()
                 outs.append(res)
-                if sample and tokens is None and self.grid.pp > 1:
+                if sample and feedback and self.grid.pp > 1:
                     sends.append(dist.isend(res, dst=self.first_rank))
         for w in sends:
             w.wait()

@@ -135,6 +135,15 @@ int dlp_sample(const float* logits, int R, int V, int ld, int top_k, float top_p
 
 int dlp_f32_to_f16(const float* in, void* out, size_t n, void* stream);
 
+/* ---- mixture of experts, decode path (graph-capturable: expert ids and weights never leave the device) ----
+ * dlp_moe_route: softmax over all experts, top-k, renormalise (n_expert <= 32) -> ids[T*k], weights[T*k].
+ * dlp_gemv_moe: one token's mat-vec against expert *expert_id_dev of a stacked [n_expert * rows_per_expert, K] weight;
+ *   outputs are multiplied by *out_scale_dev when given (DLP_OUT_ADD_F32 accumulates the weighted expert output).
+ * ref: build_moe_ffn (llama.cpp/src/llama-graph.cpp:999-1266), topk_moe_cuda (ggml-cuda/topk-moe.cu), mul_mat_vec_* _id forms. */
+int dlp_moe_route(const float* logits, int T, int n_expert, int top_k, int32_t* ids, float* weights, void* stream);
+int dlp_gemv_moe(const dlp_weight* w0, const dlp_weight* w1, const void* x, const float* norm_w, float eps, void* y, int ldy,
+                 int out_mode, const int32_t* expert_id_dev, int rows_per_expert, const float* out_scale_dev, void* stream);
+
 /* ---- tensor-parallel decode with the all-reduce fused into the mat-vecs (NVLink peer stores, no NCCL) ----
  * Each rank owns a reduce buffer [tp][T][E] fp32 and a flag array [tp] per all-reduce site, mapped by all peers
  * (dlp_symm_alloc + dlp_ipc_export / dlp_ipc_import).  A row-parallel mat-vec launched with out_mode

@@ -45,3 +45,12 @@ def test_stage_layer_ranges_follow_split_rule():
     assert sum(len(r) for r in rs) == 7 and rs[0].start == 0 and rs[-1].stop == 7
     with pytest.raises(ValueError):
         stage_layer_ranges(8, 2, [1, 2, 3])
+
+
+def test_pp2_self_feeding_decode_rounds(tmp_models):
+    """Pipeline decode where the last stage's sampled ids travel back to the first stage (no host tokens after round 0)."""
+    script = os.path.join(HERE, "mp_pp_feedback.py")
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2", "--master-addr", "127.0.0.1",
+           "--master-port", "29641", script, tmp_models[("tiny", "F16")]]
+    r = subprocess.run(cmd, capture_output=True, text=True, timeout=300, env=dict(os.environ, OMP_NUM_THREADS="2", CUDA_VISIBLE_DEVICES=""))
+    assert r.returncode == 0 and "FEEDBACK_OK" in r.stdout, r.stdout[-2000:] + r.stderr[-2000:]

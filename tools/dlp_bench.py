@@ -101,9 +101,9 @@ def main(argv=None):
 
             def run():
                 if stage:
-                    stage.decode_round([sids], [first])
-                    for _ in range(n_g - 1):
-                        stage.decode_round([sids], None)
+                    stage.decode_round([sids], [first], feedback=n_g > 1)
+                    for i in range(n_g - 1):
+                        stage.decode_round([sids], None, feedback=i < n_g - 2)
                 else:
                     eng.decode(sids, first)
                     for _ in range(n_g - 1):
