@@ -322,3 +322,41 @@ def test_fused_gemm_reduce_scatter_allgather_virtual_ranks(t, T):
             assert nmse(y_ref[:T], y[:T]) < 2e-5
             c.check_error()
         act = (act.float() * 0.7).half()
+
+
+@pytest.mark.parametrize("t", [GGMLType.F16, GGMLType.Q8_0, GGMLType.Q4_K])
+def test_moe_route_and_expert_indexed_gemv(t):
+    """Device-side MoE decode pieces: router (softmax -> top-2 -> renormalise) and mat-vecs that pick the expert's rows
+    from a stacked weight through a device-resident id, with the expert weight applied in the epilogue."""
+    nE, k, E, F = 8, 2, 512, 768
+    g = torch.Generator().manual_seed(31)
+    logits = torch.randn(3, nE, generator=g).to(DEV)
+    ids, w = ops.moe_route(logits, k)
+    pr = torch.softmax(logits, -1)
+    tw, ti = pr.topk(k, -1)
+    assert torch.equal(ids.view(3, k).long(), ti)
+    assert torch.allclose(w.view(3, k), tw / tw.sum(-1, keepdim=True), atol=1e-6)
+    # stacked experts
+    gate = torch.randn(nE * F, E, generator=g) * 0.05
+    up = torch.randn(nE * F, E, generator=g) * 0.05
+    down = torch.randn(nE * E, F, generator=g) * 0.05
+    Wg, Wu, Wd = (DeviceWeight.from_dense(m, t, DEV) for m in (gate, up, down))
+    from distributed_llm_pipeline_b200.gguf.quants import dequantize, quantize
+    import numpy as np
+    deq = lambda m: torch.from_numpy(dequantize(quantize(m.numpy(), t), t, tuple(m.shape)).astype(np.float32)).to(DEV)
+    dg, du, dd = deq(gate), deq(up), deq(down)
+    h = torch.randn(1, E, generator=g).to(DEV)
+    nw = (torch.rand(E, generator=g) + 0.5).to(DEV)
+    xn = (h * torch.rsqrt(h.pow(2).mean(-1, keepdim=True) + 1e-5) * nw).half().float()
+    href = h.clone()
+    hout = h.clone()
+    act = torch.empty(k, F, dtype=torch.float16, device=DEV)
+    for j in range(k):
+        e = int(ids[j])
+        ops.gemv_moe(Wg, h, act[j:j + 1], "swiglu", ids[j:j + 1], F, w_up=Wu, norm_w=nw, eps=1e-5)
+        a_ref = torch.nn.functional.silu(xn @ dg[e * F:(e + 1) * F].T) * (xn @ du[e * F:(e + 1) * F].T)
+        assert nmse(a_ref, act[j:j + 1]) < (3e-4 if t.name.startswith("Q") else 2e-5)
+        href += float(w[j]) * (act[j:j + 1].float() @ dd[e * E:(e + 1) * E].T)
+    for j in range(k):
+        ops.gemv_moe(Wd, act[j:j + 1], hout, "add", ids[j:j + 1], E, out_scale=w[j:j + 1])
+    assert nmse(href, hout) < (1e-4 if t.name.startswith("Q") else 1e-6)
