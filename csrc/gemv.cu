@@ -226,7 +226,7 @@ __global__ void __launch_bounds__(256) gemv_dense_kernel(const GemvParams p) {
 //     they reduce the current one - the load stream never waits for the math;
 //   * the first unit is requested before griddepcontrol.wait and before the prologue;
 //   * per-unit partial sums go to shared memory and are combined in a fixed order (deterministic) after one barrier.
-template <int NT, bool BF16, int U>
+template <int NT, bool BF16, int U, int DEPTH>
 __global__ void __launch_bounds__(256, 2) gemv_dense_v3_kernel(const GemvParams p) {
     extern __shared__ __align__(16) uint8_t gv_smem[];
     const int K = p.w0.K, N = p.w0.N;
@@ -248,7 +248,7 @@ __global__ void __launch_bounds__(256, 2) gemv_dense_v3_kernel(const GemvParams 
     const int g_hi = (int)(((long long)groups_total * (blockIdx.x + 1)) / gridDim.x);
     const int n_units = (g_hi - g_lo) * KC;
 
-    uint4 buf[2][2][U];   // [double buffer][stream][load]
+    uint4 buf[DEPTH][2][U];   // [ring slot][stream][load]
     int roff = 0;         // expert row offset (MoE), known only after the router kernel has finished
     auto issue = [&](int u, int b) {
         const int g = g_lo + u / KC, c = u % KC;
@@ -303,31 +303,39 @@ __global__ void __launch_bounds__(256, 2) gemv_dense_v3_kernel(const GemvParams 
             }
     };
 
-    int u = warp;                              // the first round is assigned statically so that it can start right now
-    if (threadIdx.x == 0) next_unit = 8;
+    int uu[DEPTH];
     const bool dyn_rows = p.row_off_dev != nullptr;
-    if (!dyn_rows && u < n_units) issue(u, 0); // weights are static: requested before the predecessor has finished
+#pragma unroll
+    for (int d = 0; d < DEPTH; ++d) {          // the first DEPTH rounds are assigned statically so that they can start right now:
+        uu[d] = warp + 8 * d;                  // weights are static, requested before the predecessor has finished
+        if (!dyn_rows && uu[d] < n_units) issue(uu[d], d);
+    }
+    if (threadIdx.x == 0) next_unit = 8 * DEPTH;
     pdl_wait();
     if (dyn_rows) {
         roff = (*p.row_off_dev) * p.row_off_mul;
-        if (u < n_units) issue(u, 0);
+#pragma unroll
+        for (int d = 0; d < DEPTH; ++d)
+            if (uu[d] < n_units) issue(uu[d], d);
     }
     const float oscale = p.out_scale_dev ? *p.out_scale_dev : 1.f;
     stage_x<NT>(p, K, xs, red);                // (ends with __syncthreads: next_unit is visible)
 
-    while (u < n_units) {                      // software pipeline, unrolled by two for static register indexing
-        int un = 0;
-        if (lane == 0) un = atomicAdd(&next_unit, 1);
-        un = __shfl_sync(0xffffffffu, un, 0);
-        if (un < n_units) issue(un, 1);
-        reduce(u, 0);
-        if (un >= n_units) break;
-        int u2 = 0;
-        if (lane == 0) u2 = atomicAdd(&next_unit, 1);
-        u2 = __shfl_sync(0xffffffffu, u2, 0);
-        if (u2 < n_units) issue(u2, 0);
-        reduce(un, 1);
-        u = u2;
+    for (;;) {                                 // ring of DEPTH prefetched units per warp, refilled from the shared counter
+        bool did = false;
+#pragma unroll
+        for (int d = 0; d < DEPTH; ++d) {
+            if (uu[d] < n_units) {
+                reduce(uu[d], d);
+                int un = 0;
+                if (lane == 0) un = atomicAdd(&next_unit, 1);
+                un = __shfl_sync(0xffffffffu, un, 0);
+                uu[d] = un;
+                if (un < n_units) issue(un, d);
+                did = true;
+            }
+        }
+        if (!did) break;
     }
     pdl_launch_dependents();
     __syncthreads();
@@ -1009,20 +1017,29 @@ int gemv(const GemvParams& p, int wtype, cudaStream_t stream) {
         }
     }
     DLP_REQUIRE(p.row_off_dev == nullptr || (T == 1 && K % 256 == 0), "gemv: expert-indexed weights need T == 1");
-    static int use_v3 = -1;
-    if (use_v3 < 0) { const char* e = getenv("DLP_GEMV_V3"); use_v3 = (e && e[0] == '0') ? 0 : 1; }
+    static int use_v3 = -1, v3_cfg = 0;
+    if (use_v3 < 0) {
+        const char* e = getenv("DLP_GEMV_V3");
+        use_v3 = (e && e[0] == '0') ? 0 : 1;
+        const char* c = getenv("DLP_GEMV_UD");   // "42" = 4 loads/row/unit x 2 units in flight (default), "24" = 2 x 4
+        v3_cfg = (c && c[0] == '2') ? 1 : 0;
+    }
     if (use_v3 && (wtype == W_F16 || wtype == W_BF16)) {
-        const int U = (K % 1024 == 0) ? 4 : (K % 512 == 0) ? 2 : 1;
+        int U = (K % 1024 == 0) ? 4 : (K % 512 == 0) ? 2 : 1;
+        if (v3_cfg == 1 && U == 4) U = 2;
         const bool bf = wtype == W_BF16;
         const size_t xsm = smem;
-#define DLP_V3(NT_, U_)                                                                                           \
-    return bf ? launch_gemv_v3(gemv_dense_v3_kernel<NT_, true, U_>, p, U_, xsm, stream)                            \
-              : launch_gemv_v3(gemv_dense_v3_kernel<NT_, false, U_>, p, U_, xsm, stream);
+#define DLP_V3(NT_, U_, D_)                                                                                       \
+    return bf ? launch_gemv_v3(gemv_dense_v3_kernel<NT_, true, U_, D_>, p, U_, xsm, stream)                        \
+              : launch_gemv_v3(gemv_dense_v3_kernel<NT_, false, U_, D_>, p, U_, xsm, stream);
+#define DLP_V3_T(NT_)                                                                                             \
+    if (U == 4) { DLP_V3(NT_, 4, 2) } else if (U == 2 && v3_cfg == 1) { DLP_V3(NT_, 2, 4) } else if (U == 2) { DLP_V3(NT_, 2, 2) } else { DLP_V3(NT_, 1, 4) }
         if (xsm + 8192 <= 100 * 1024) {   // x (+ partials) must fit next to a second resident CTA
-            if (T == 1) { if (U == 4) { DLP_V3(1, 4) } else if (U == 2) { DLP_V3(1, 2) } else { DLP_V3(1, 1) } }
-            if (T == 2) { if (U == 4) { DLP_V3(2, 4) } else if (U == 2) { DLP_V3(2, 2) } else { DLP_V3(2, 1) } }
-            if (T == 4) { if (U == 4) { DLP_V3(4, 4) } else if (U == 2) { DLP_V3(4, 2) } else { DLP_V3(4, 1) } }
+            if (T == 1) { DLP_V3_T(1) }
+            if (T == 2) { DLP_V3_T(2) }
+            if (T == 4) { DLP_V3_T(4) }
         }
+#undef DLP_V3_T
 #undef DLP_V3
     }
     static int use_qv3 = -1;
