@@ -1,0 +1,57 @@
+"""Aux tools: quantize, gguf-split/merge, tokenize, perplexity, bench, cli (CPU, tiny model)."""
+import os
+import subprocess
+import sys
+
+import numpy as np
+
+from distributed_llm_pipeline_b200.gguf import GGMLType, open_gguf
+
+REPO = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _run(tool, *args):
+    r = subprocess.run([sys.executable, os.path.join(REPO, "tools", tool), *args], capture_output=True, text=True, timeout=300,
+                       env=dict(os.environ, CUDA_VISIBLE_DEVICES=""))
+    assert r.returncode == 0, r.stdout[-1500:] + r.stderr[-1500:]
+    return r.stdout
+
+
+def test_quantize_tool(tmp_models, tmp_path):
+    dst = str(tmp_path / "q.gguf")
+    _run("dlp_quantize.py", tmp_models[("tiny", "F16")], dst, "Q4_K_M")
+    f = open_gguf(dst)
+    assert f.tensors["blk.0.ffn_gate.weight"].ggml_type == GGMLType.Q4_K
+    assert f.tensors["output.weight"].ggml_type == GGMLType.Q6_K
+    assert f.tensors["blk.0.attn_norm.weight"].ggml_type == GGMLType.F32
+    src = open_gguf(tmp_models[("tiny", "F16")])
+    a, b = src.array("blk.0.ffn_up.weight"), f.array("blk.0.ffn_up.weight")
+    assert ((a - b) ** 2).sum() / (a ** 2).sum() < 1e-2
+    assert f.metadata["tokenizer.ggml.tokens"] == src.metadata["tokenizer.ggml.tokens"]
+
+
+def test_gguf_split_and_merge(tmp_models, tmp_path):
+    src = tmp_models[("tiny", "Q8_0")]
+    out = _run("dlp_gguf_split.py", "--split", "--split-max-tensors", "8", src, str(tmp_path / "shard")).split()
+    assert len(out) == 3 and out[0].endswith("-00001-of-00003.gguf")
+    whole, parts = open_gguf(src), open_gguf(out[0])
+    assert set(whole.tensors) == set(parts.tensors)
+    for n in whole.tensors:
+        assert np.array_equal(whole.raw(n), parts.raw(n))
+    merged = str(tmp_path / "merged.gguf")
+    _run("dlp_gguf_split.py", "--merge", out[0], merged)
+    m = open_gguf(merged)
+    assert set(m.tensors) == set(whole.tensors) and "split.no" not in m.metadata
+
+
+def test_tokenize_perplexity_bench_cli(tmp_models):
+    model = tmp_models[("tiny", "F16")]
+    out = _run("dlp_tokenize.py", "-m", model, "-p", "hello world", "--ids")
+    assert out.strip().startswith("[1,")
+    out = _run("dlp_perplexity.py", "-m", model, "--device", "cpu", "-c", "32", "--chunks", "1")
+    ppl = float(out.strip().split("PPL = ")[-1].split()[0])
+    assert 50 < ppl < 5000                 # random-init model: PPL of the order of the vocabulary size (512)
+    out = _run("dlp_bench.py", "-m", model, "--device", "cpu", "-p", "16", "-n", "4", "-r", "1", "-o", "json")
+    assert '"test": "pp16"' in out and '"test": "tg4"' in out
+    out = _run("dlp_cli.py", "-m", model, "--device", "cpu", "-p", "hi", "-n", "4", "-st", "--temp", "0")
+    assert len(out) > 0

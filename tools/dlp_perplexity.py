@@ -1,0 +1,58 @@
+#!/usr/bin/env python
+"""dlp-perplexity: perplexity of a token stream under a GGUF model (chunks of n_ctx tokens, second half of each chunk scored).
+
+Parity: `llama-perplexity` (llama.cpp/tools/perplexity/perplexity.cpp) default strided mode.  Works with random-init models
+too (then PPL ~ vocab size) - used as a whole-model numerics check between back-ends / quantisations.
+"""
+import argparse
+import math
+import os
+import sys
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import torch  # noqa: E402
+
+
+def main(argv=None):
+    ap = argparse.ArgumentParser(description=__doc__.splitlines()[0])
+    ap.add_argument("-m", "--model", required=True)
+    ap.add_argument("-f", "--file", default=None, help="text file (tokenised with the model's tokenizer); default: synthetic ids")
+    ap.add_argument("-c", "--ctx-size", type=int, default=128)
+    ap.add_argument("--chunks", type=int, default=4)
+    ap.add_argument("--device", default="cuda")
+    a = ap.parse_args(argv)
+    from distributed_llm_pipeline_b200.gguf import open_gguf
+    from distributed_llm_pipeline_b200.models.llama import LlamaEngine
+    from distributed_llm_pipeline_b200.models.weights import load_weights
+    from distributed_llm_pipeline_b200.utils.tokenizer import Tokenizer
+    dev = a.device if (a.device != "cuda" or torch.cuda.is_available()) else "cpu"
+    f = open_gguf(a.model)
+    w = load_weights(f, dev)
+    eng = LlamaEngine(w, n_ctx=a.ctx_size, max_seqs=1, page_size=64 if dev != "cpu" else 16, max_batch_tokens=a.ctx_size)
+    if a.file:
+        ids = Tokenizer(f.metadata).encode(open(a.file).read())
+    else:
+        g = torch.Generator().manual_seed(0)
+        ids = torch.randint(3, w.cfg.vocab_size, (a.ctx_size * a.chunks,), generator=g).tolist()
+    nll, count = 0.0, 0
+    n_chunks = min(a.chunks, len(ids) // a.ctx_size)
+    for c in range(n_chunks):
+        chunk = ids[c * a.ctx_size:(c + 1) * a.ctx_size]
+        sid = eng.alloc_seq()
+        half = a.ctx_size // 2
+        eng.prefill(sid, chunk[:half])
+        for i in range(half, a.ctx_size):            # teacher-forced decode over the second half
+            logits = eng.decode([sid], [chunk[i - 1]] if i > half else [chunk[half - 1]], sample=False)[0] if i > half else None
+            if logits is None:
+                eng.truncate_seq(sid, half - 1)
+                logits = eng.decode([sid], [chunk[half - 1]], sample=False)[0]
+            lp = torch.log_softmax(logits.float(), -1)[chunk[i]]
+            nll -= float(lp)
+            count += 1
+        eng.free_seq(sid)
+        print(f"[{c + 1}/{n_chunks}] running PPL = {math.exp(nll / count):.4f}", flush=True)
+    print(f"Final estimate: PPL = {math.exp(nll / max(1, count)):.4f} over {count} tokens")
+
+
+if __name__ == "__main__":
+    main()

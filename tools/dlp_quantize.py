@@ -1,0 +1,56 @@
+#!/usr/bin/env python
+"""dlp-quantize: re-encode a GGUF checkpoint to another file type (F16 / BF16 / Q8_0 / Q6_K / Q4_K_M / Q5_K_M).
+
+Parity: `llama-quantize` (`llama.cpp/tools/quantize`, mix rules `src/llama-quant.cpp:302-405`).  Tensor-type selection is the
+same recipe `gguf/synth.py` uses; encoders are the closed-form ones of `gguf/quants.py` (no importance matrix).
+"""
+import argparse
+import os
+import sys
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import numpy as np  # noqa: E402
+
+from distributed_llm_pipeline_b200.gguf import GGMLType, GGUFWriter, open_gguf, quantize  # noqa: E402
+from distributed_llm_pipeline_b200.gguf.constants import FTYPE, BLOCK_GEOMETRY  # noqa: E402
+from distributed_llm_pipeline_b200.gguf.synth import tensor_type_for  # noqa: E402
+from distributed_llm_pipeline_b200.models.config import config_from_gguf  # noqa: E402
+
+
+def main(argv=None):
+    ap = argparse.ArgumentParser(description=__doc__.splitlines()[0])
+    ap.add_argument("src")
+    ap.add_argument("dst")
+    ap.add_argument("ftype", choices=sorted(FTYPE))
+    a = ap.parse_args(argv)
+    f = open_gguf(a.src)
+    cfg = config_from_gguf(f.metadata, f.tensors)
+    w = GGUFWriter(a.dst)
+    src_file = f.files[0]
+    for key, val in f.metadata.items():
+        if key == "general.file_type":
+            continue
+        w.add(key, val, src_file.metadata_types[key]) if not isinstance(val, (list, np.ndarray)) else w.add(key, val)
+    w.add("general.file_type", FTYPE[a.ftype])
+    n_in = n_out = 0
+    for name, info in f.tensors.items():
+        il = int(name.split(".")[1]) if name.startswith("blk.") else 0
+        want = tensor_type_for(name, a.ftype, il, cfg) if len(info.shape) > 1 else GGMLType.F32
+        per, _ = BLOCK_GEOMETRY[want]
+        if info.shape[-1] % per:
+            want = GGMLType.F16          # rows that do not fill a block stay dense (as llama-quantize does)
+        n_in += info.nbytes
+
+        def produce(name=name, want=want, info=info):
+            if want == info.ggml_type:
+                return np.ascontiguousarray(f.raw(name)).reshape(-1)
+            return quantize(f.array(name).reshape(-1, info.shape[-1]), want)
+
+        w.add_tensor(name, info.shape, want, produce)
+    w.write()
+    n_out = os.path.getsize(a.dst)
+    print(f"{a.src} -> {a.dst}  [{a.ftype}]  {n_in / 2**20:.1f} MiB -> {n_out / 2**20:.1f} MiB")
+
+
+if __name__ == "__main__":
+    main()
