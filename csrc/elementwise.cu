@@ -132,10 +132,15 @@ int rmsnorm(float* h, const float* delta, const float* w, __half* out, int T, in
 //   qkv   : [T, (Hq + 2*Hkv) * D]  fp32 or fp16 (row = q heads | k heads | v heads)
 //   q_out : [T, Hq * D] fp16 (rotated, pre-scaled by q_scale)
 //   k/v cache : [n_pages][Hkv][page_size][D] fp16 ; slot[t] = page * page_size + offset   (slot < 0 => skip write)
-template <typename InT>
+//   EX variant (other architecture families): bias [H*D] added to q/k/v before anything else (qwen2), and a per-head
+//   RMSNorm over D with weights qn / kn applied to q / k heads before the rotation (qwen3).  A head's D/2 pairs sit in
+//   D/64 consecutive warps of one CTA (256 % (D/2) == 0), so the sum of squares is a shuffle plus a few smem words.
+template <typename InT, bool EX>
 __global__ void rope_kv_kernel(const InT* __restrict__ qkv, const int* __restrict__ pos, const int* __restrict__ slot,
                                const float* __restrict__ inv_freq, __half* __restrict__ q_out, __half* __restrict__ kc,
-                               __half* __restrict__ vc, int Hq, int Hkv, int D, int n_rot, int page_size, int neox, float q_scale) {
+                               __half* __restrict__ vc, int Hq, int Hkv, int D, int n_rot, int page_size, int neox, float q_scale,
+                               const float* __restrict__ bias, const float* __restrict__ qn, const float* __restrict__ kn,
+                               float eps) {
     // one (head, pair) per thread: grid = (T, ceil(H * D/2 / 256)) so that even a single decode token spreads over
     // a dozen CTAs and every load is issued at once (a serial per-thread loop here is pure latency)
     const int t = blockIdx.x;
@@ -144,12 +149,13 @@ __global__ void rope_kv_kernel(const InT* __restrict__ qkv, const int* __restric
     const int idx = blockIdx.y * blockDim.x + threadIdx.x;
     pdl_wait();
     pdl_launch_dependents();
-    if (idx >= H * half_d) return;
+    const bool live = idx < H * half_d;
+    if (!EX && !live) return;
     const float p = (float)pos[t];
     const int sl = slot[t];
     const int page = sl >= 0 ? sl / page_size : 0, off = sl >= 0 ? sl % page_size : 0;
     const InT* row = qkv + (size_t)t * H * D;
-    const int hh = idx / half_d, i = idx % half_d;
+    const int hh = live ? idx / half_d : 0, i = idx % half_d;
     int d0, d1;
     if (neox) { d0 = i; d1 = i + n_rot / 2; } else { d0 = 2 * i; d1 = 2 * i + 1; }
     const bool rot = hh < Hq + Hkv && (neox ? i < n_rot / 2 : 2 * i < n_rot);
@@ -157,7 +163,31 @@ __global__ void rope_kv_kernel(const InT* __restrict__ qkv, const int* __restric
         d0 = n_rot + 2 * (i - n_rot / 2);
         d1 = d0 + 1;
     }
-    float x0 = (float)row[hh * D + d0], x1 = (float)row[hh * D + d1];
+    float x0 = live ? (float)row[hh * D + d0] : 0.f, x1 = live ? (float)row[hh * D + d1] : 0.f;
+    if (EX) {
+        if (bias != nullptr && live) { x0 += bias[hh * D + d0]; x1 += bias[hh * D + d1]; }
+        if (qn != nullptr) {
+            __shared__ float wsum[8];
+            float ss = x0 * x0 + x1 * x1;
+            if (half_d >= 32) {
+                ss = warp_sum(ss);
+                if ((threadIdx.x & 31) == 0) wsum[threadIdx.x >> 5] = ss;
+                __syncthreads();
+                const int wph = half_d / 32, w0 = (threadIdx.x >> 5) / wph * wph;
+                ss = 0.f;
+                for (int w = 0; w < wph; ++w) ss += wsum[w0 + w];
+            } else {
+                for (int o = half_d / 2; o > 0; o >>= 1) ss += __shfl_xor_sync(0xffffffffu, ss, o);
+            }
+            if (hh < Hq + Hkv) {
+                const float r = rsqrtf(ss / (float)D + eps);
+                const float* nw = hh < Hq ? qn : kn;
+                x0 *= r * nw[d0];
+                x1 *= r * nw[d1];
+            }
+        }
+        if (!live) return;
+    }
     if (rot) {
         float sn, cs;
         sincosf(p * inv_freq[i], &sn, &cs);
@@ -179,12 +209,16 @@ __global__ void rope_kv_kernel(const InT* __restrict__ qkv, const int* __restric
 
 int rope_kv(const void* qkv, int qkv_is_f16, const int* pos, const int* slot, const float* inv_freq, __half* q_out,
             __half* kc, __half* vc, int T, int Hq, int Hkv, int D, int n_rot, int page_size, int neox, float q_scale,
-            cudaStream_t s) {
+            cudaStream_t s, const float* bias, const float* qn, const float* kn, float eps) {
     DLP_REQUIRE(T > 0 && D % 2 == 0 && n_rot <= D && n_rot % 2 == 0, "rope_kv: bad shape");
-    if (qkv_is_f16)
-        DLP_CHECK_CUDA(launch_pdl(rope_kv_kernel<__half>, dim3(T, ((Hq + 2 * Hkv) * (D / 2) + 255) / 256), dim3(256), 0, s, (const __half*)qkv, pos, slot, inv_freq, q_out, kc, vc, Hq, Hkv, D, n_rot, page_size, neox, q_scale));
-    else
-        DLP_CHECK_CUDA(launch_pdl(rope_kv_kernel<float>, dim3(T, ((Hq + 2 * Hkv) * (D / 2) + 255) / 256), dim3(256), 0, s, (const float*)qkv, pos, slot, inv_freq, q_out, kc, vc, Hq, Hkv, D, n_rot, page_size, neox, q_scale));
+    DLP_REQUIRE((qn == nullptr) == (kn == nullptr), "rope_kv: q/k norm weights come as a pair");
+    const bool ex = bias != nullptr || qn != nullptr;
+    if (qn != nullptr) DLP_REQUIRE(256 % (D / 2) == 0 && (D / 2 >= 32 || (D / 2 & (D / 2 - 1)) == 0), "rope_kv: qk-norm needs D/2 | 256 (D=%d)", D);
+    const dim3 grid(T, ((Hq + 2 * Hkv) * (D / 2) + 255) / 256);
+#define DLP_ROPE_LAUNCH(TY, EXF) DLP_CHECK_CUDA(launch_pdl(rope_kv_kernel<TY, EXF>, grid, dim3(256), 0, s, (const TY*)qkv, pos, slot, inv_freq, q_out, kc, vc, Hq, Hkv, D, n_rot, page_size, neox, q_scale, bias, qn, kn, eps))
+    if (qkv_is_f16) { if (ex) DLP_ROPE_LAUNCH(__half, true); else DLP_ROPE_LAUNCH(__half, false); }
+    else            { if (ex) DLP_ROPE_LAUNCH(float, true);  else DLP_ROPE_LAUNCH(float, false); }
+#undef DLP_ROPE_LAUNCH
     return 0;
 }
 

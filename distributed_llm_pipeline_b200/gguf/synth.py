@@ -28,7 +28,8 @@ def use_more_bits(i_layer: int, n_layer: int) -> bool:
 
 def tensor_type_for(name: str, ftype: str, i_layer: int, cfg: ModelConfig) -> GGMLType:
     """Per-tensor storage type for a given file type."""
-    if name.endswith("_norm.weight") or name == "rope_freqs.weight" or name.endswith("ffn_gate_inp.weight"):
+    if name.endswith("_norm.weight") or name == "rope_freqs.weight" or name.endswith("ffn_gate_inp.weight") \
+            or name.endswith(".bias"):
         return GGMLType.F32
     if ftype == "F32":
         return GGMLType.F32
@@ -106,15 +107,25 @@ def _tensor_plan(cfg: ModelConfig, rope_freqs: bool):
         plan.append(("rope_freqs.weight", (cfg.rope_dim // 2,), -1, 0.0))
     for il in range(cfg.n_layer):
         p = f"blk.{il}."
+        plan.append((p + "attn_norm.weight", (E,), il, 0.0))
+        if cfg.fused_qkv:
+            plan.append((p + "attn_qkv.weight", (cfg.q_dim + 2 * cfg.kv_dim, E), il, 0.02))
+        else:
+            plan += [(p + "attn_q.weight", (cfg.q_dim, E), il, 0.02),
+                     (p + "attn_k.weight", (cfg.kv_dim, E), il, 0.02),
+                     (p + "attn_v.weight", (cfg.kv_dim, E), il, 0.02)]
+        if cfg.qkv_bias:
+            plan += [(p + "attn_q.bias", (cfg.q_dim,), il, 0.05), (p + "attn_k.bias", (cfg.kv_dim,), il, 0.05),
+                     (p + "attn_v.bias", (cfg.kv_dim,), il, 0.05)]
+        if cfg.qk_norm:
+            plan += [(p + "attn_q_norm.weight", (cfg.head_dim,), il, 0.0), (p + "attn_k_norm.weight", (cfg.head_dim,), il, 0.0)]
         plan += [
-            (p + "attn_norm.weight", (E,), il, 0.0),
-            (p + "attn_q.weight", (cfg.q_dim, E), il, 0.02),
-            (p + "attn_k.weight", (cfg.kv_dim, E), il, 0.02),
-            (p + "attn_v.weight", (cfg.kv_dim, E), il, 0.02),
             (p + "attn_output.weight", (E, cfg.q_dim), il, 0.02),
             (p + "ffn_norm.weight", (E,), il, 0.0),
         ]
-        if cfg.is_moe:
+        if cfg.fused_qkv:
+            plan += [(p + "ffn_up.weight", (2 * F, E), il, 0.02), (p + "ffn_down.weight", (E, F), il, 0.02)]
+        elif cfg.is_moe:
             plan += [
                 (p + "ffn_gate_inp.weight", (cfg.n_expert, E), il, 0.02),
                 (p + "ffn_gate_exps.weight", (cfg.n_expert, F, E), il, 0.02),
@@ -184,6 +195,8 @@ def write_synthetic_gguf(path: str, cfg: ModelConfig, ftype: str = "F16", seed: 
                 if name == "rope_freqs.weight":
                     return np.ones(shape, np.float32).view(np.uint8).reshape(-1)
                 return (1.0 + 0.1 * rng.standard_normal(n, dtype=np.float32)).astype("<f4").view(np.uint8)
+            if name.endswith(".bias"):
+                return (rng.standard_normal(n, dtype=np.float32) * std).astype("<f4").view(np.uint8)
             if exact:
                 x = rng.standard_normal(n, dtype=np.float32) * std
                 return quantize(x.reshape(-1, shape[-1]), ttype)

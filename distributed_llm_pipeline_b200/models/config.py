@@ -32,6 +32,9 @@ class ModelConfig:
     bos_id: int = 1
     eos_id: int = 2
     tie_embeddings: bool = False
+    qkv_bias: bool = False     # qwen2: bias on Wq/Wk/Wv
+    qk_norm: bool = False      # qwen3: per-head RMSNorm on Q and K before RoPE
+    fused_qkv: bool = False    # phi3: one attn_qkv tensor and one [2*n_ff] ffn_up (gate | up) tensor in the file
 
     @property
     def n_gqa(self) -> int:
@@ -68,6 +71,27 @@ PRESETS: dict[str, ModelConfig] = {
     "tiny-moe": ModelConfig(name="tiny-moe", vocab_size=512, n_embd=256, n_layer=2, n_head=4, n_head_kv=2,
                             head_dim=64, n_ff=256, n_ctx_train=512, rope_theta=10000.0, rope_dim=64, n_expert=4,
                             n_expert_used=2),
+    # one tiny config per extra architecture family (llama.cpp/src/models/{qwen2,qwen3,phi3}.cpp)
+    "tiny-qwen2": ModelConfig(name="tiny-qwen2", arch="qwen2", vocab_size=512, n_embd=256, n_layer=2, n_head=4, n_head_kv=2,
+                              head_dim=64, n_ff=512, n_ctx_train=512, rope_theta=10000.0, rope_dim=64, rope_neox=True,
+                              qkv_bias=True),
+    "tiny-qwen3": ModelConfig(name="tiny-qwen3", arch="qwen3", vocab_size=512, n_embd=256, n_layer=2, n_head=4, n_head_kv=2,
+                              head_dim=128, n_ff=512, n_ctx_train=512, rope_theta=10000.0, rope_dim=128, rope_neox=True,
+                              qk_norm=True),
+    "tiny-phi3": ModelConfig(name="tiny-phi3", arch="phi3", vocab_size=512, n_embd=256, n_layer=2, n_head=4, n_head_kv=4,
+                             head_dim=64, n_ff=512, n_ctx_train=512, rope_theta=10000.0, rope_dim=64, rope_neox=True,
+                             fused_qkv=True),
+    "qwen2.5-7b": ModelConfig(name="qwen2.5-7b", arch="qwen2", vocab_size=152064, n_embd=3584, n_layer=28, n_head=28,
+                              n_head_kv=4, head_dim=128, n_ff=18944, n_ctx_train=32768, rms_eps=1e-6, rope_theta=1000000.0,
+                              rope_dim=128, rope_neox=True, qkv_bias=True, bos_id=151643, eos_id=151645),
+    "qwen3-8b": ModelConfig(name="qwen3-8b", arch="qwen3", vocab_size=151936, n_embd=4096, n_layer=36, n_head=32,
+                            n_head_kv=8, head_dim=128, n_ff=12288, n_ctx_train=40960, rms_eps=1e-6, rope_theta=1000000.0,
+                            rope_dim=128, rope_neox=True, qk_norm=True, bos_id=151643, eos_id=151645),
+    "mistral-7b": ModelConfig(name="mistral-7b", vocab_size=32000, n_embd=4096, n_layer=32, n_head=32, n_head_kv=8,
+                              head_dim=128, n_ff=14336, n_ctx_train=32768, rope_theta=10000.0, rope_dim=128),
+    "phi-3-medium": ModelConfig(name="phi-3-medium", arch="phi3", vocab_size=32064, n_embd=5120, n_layer=40, n_head=40,
+                                n_head_kv=10, head_dim=128, n_ff=17920, n_ctx_train=4096, rope_theta=10000.0, rope_dim=128,
+                                rope_neox=True, fused_qkv=True),
     "tinyllama-1.1b": ModelConfig(name="tinyllama-1.1b", vocab_size=32000, n_embd=2048, n_layer=22, n_head=32,
                                   n_head_kv=4, head_dim=64, n_ff=5632, n_ctx_train=2048, rope_theta=10000.0,
                                   rope_dim=64),
@@ -83,6 +107,12 @@ PRESETS: dict[str, ModelConfig] = {
 }
 
 
+# GGUF `general.architecture` values this engine runs.  llama covers LLaMA 1-3, Mistral and Mixtral (MoE tensors present);
+# qwen2 adds Q/K/V biases, qwen3 per-head Q/K RMSNorm, phi3 fused QKV / gate-up tensors; the last three rotate half-split
+# ("neox") pairs (`llama.cpp/src/llama-model.cpp` llama_model_rope_type).
+SUPPORTED_ARCHS = {"llama", "qwen2", "qwen3", "phi3"}
+
+
 def preset(name: str, **overrides) -> ModelConfig:
     if name not in PRESETS:
         raise KeyError(f"unknown model preset {name!r}; known: {sorted(PRESETS)}")
@@ -92,8 +122,8 @@ def preset(name: str, **overrides) -> ModelConfig:
 def config_from_gguf(meta: dict[str, Any], tensors: dict | None = None) -> ModelConfig:
     """Build a ModelConfig from GGUF metadata (keys as in `llama-arch.cpp:128-268`)."""
     arch = meta.get("general.architecture", "llama")
-    if arch != "llama":
-        raise NotImplementedError(f"architecture {arch!r} not supported (llama / mixtral-as-llama only)")
+    if arch not in SUPPORTED_ARCHS:
+        raise NotImplementedError(f"architecture {arch!r} not supported (supported: {sorted(SUPPORTED_ARCHS)})")
 
     def g(key, default=None):
         return meta.get(f"{arch}.{key}", default)
@@ -120,7 +150,10 @@ def config_from_gguf(meta: dict[str, Any], tensors: dict | None = None) -> Model
         n_layer=int(g("block_count")), n_head=n_head, n_head_kv=n_head_kv, head_dim=head_dim,
         n_ff=int(g("feed_forward_length")), n_ctx_train=int(g("context_length", 2048)),
         rms_eps=float(g("attention.layer_norm_rms_epsilon", 1e-5)), rope_theta=float(g("rope.freq_base", 10000.0)),
-        rope_dim=int(g("rope.dimension_count", head_dim)), rope_neox=False, rope_scale_linear=scale,
+        rope_dim=int(g("rope.dimension_count", head_dim)), rope_neox=arch != "llama", rope_scale_linear=scale,
+        qkv_bias=arch == "qwen2" or (tensors is not None and "blk.0.attn_q.bias" in tensors),
+        qk_norm=arch == "qwen3" or (tensors is not None and "blk.0.attn_q_norm.weight" in tensors),
+        fused_qkv=arch == "phi3" or (tensors is not None and "blk.0.attn_qkv.weight" in tensors),
         n_expert=int(g("expert_count", 0) or 0), n_expert_used=int(g("expert_used_count", 0) or 0),
         bos_id=int(meta.get("tokenizer.ggml.bos_token_id", 1)), eos_id=int(meta.get("tokenizer.ggml.eos_token_id", 2)),
         tie_embeddings=tie)

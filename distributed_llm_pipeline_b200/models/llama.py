@@ -188,6 +188,13 @@ class LlamaEngine:
             self.scratch = torch.empty(need, dtype=torch.uint8, device=self.device)
         return self.scratch
 
+    def _rope(self, il: int, qkv: torch.Tensor, T: int) -> torch.Tensor:
+        """(+bias, per-head Q/K norm,) RoPE, paged K/V write: one launch for every architecture family."""
+        lw = self.w.layers[il]
+        return ops.rope_kv(qkv, self.pos[:T], self.slot[:T], self.inv_freq, self.kv.k[il], self.kv.v[il], self.Hq, self.Hkv,
+                           self.D, self.cfg.rope_neox, q_out=self.q[:T], bias=lw.qkv_bias, q_norm=lw.q_norm, k_norm=lw.k_norm,
+                           eps=self.cfg.rms_eps)
+
     # ---- one transformer layer over T tokens held in the static buffers ------------------------
     def _layer(self, il: int, T: int, attn_fn):
         lw, cfg, comm = self.w.layers[il], self.cfg, self.comm
@@ -200,8 +207,7 @@ class LlamaEngine:
         else:
             xn = ops.rmsnorm(h, lw.attn_norm, cfg.rms_eps, out=self.xn[:T])
             qkv = ops.linear(lw.wqkv, xn, "f16", out=self.qkv16[:T], scratch=self._scratch_for(lw.wqkv))
-        q = ops.rope_kv(qkv, self.pos[:T], self.slot[:T], self.inv_freq, self.kv.k[il], self.kv.v[il], self.Hq, self.Hkv,
-                        self.D, cfg.rope_neox, q_out=self.q[:T])
+        q = self._rope(il, qkv, T)
         att = attn_fn(il, q, T)
         if tp:
             d = ops.linear(lw.wo, att, "f32", out=self.delta[:T], scratch=self._scratch_for(lw.wo))
@@ -241,8 +247,7 @@ class LlamaEngine:
             self.cur ^= 1
         else:
             c.gemv(lw.wqkv, hin, ops.OUT_F32, T, out=self.qkv32[:T], norm_w=lw.attn_norm, eps=cfg.rms_eps)
-        q = ops.rope_kv(self.qkv32[:T], self.pos[:T], self.slot[:T], self.inv_freq, self.kv.k[il], self.kv.v[il], self.Hq,
-                        self.Hkv, self.D, cfg.rope_neox, q_out=self.q[:T])
+        q = self._rope(il, self.qkv32[:T], T)
         att = attn_fn(il, q, T)
         c.gemv(lw.wo, att, 4, T, ar_out=c.ar_out(2 * li))
         act = c.gemv(lw.w_gate, self.hb[self.cur], ops.OUT_SWIGLU_F16, T, out=self.act[:T], w_up=lw.w_up, norm_w=lw.ffn_norm,
@@ -357,8 +362,7 @@ class LlamaEngine:
             lw = w.layers[il]
             c.sp_norm_ag(hs, rows, lw.attn_norm, cfg.rms_eps, g=0, red=pending)
             c.sp_gemm(lw.wqkv, c.sp_gather_view(0, Tp), E, Tp, rows, 0, y=self.qkv16[:Tp], x_from_g=0)
-            q = ops.rope_kv(self.qkv16[:T], self.pos[:T], self.slot[:T], self.inv_freq, self.kv.k[il], self.kv.v[il], self.Hq, self.Hkv,
-                            self.D, cfg.rope_neox, q_out=self.q[:T])
+            q = self._rope(il, self.qkv16[:T], T)
             attn_fn(il, q, T)
             c.sp_gemm(lw.wo, self.att[:Tp], qd, Tp, rows, 5, rs_to=0)
             c.sp_norm_ag(hs, rows, lw.ffn_norm, cfg.rms_eps, g=1, red=0)

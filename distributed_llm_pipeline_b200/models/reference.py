@@ -88,9 +88,18 @@ class ReferenceModel:
         c, w = self.cfg, self.w
         p = f"blk.{il}."
         T = x.shape[0]
-        q = (x @ w[p + "attn_q.weight"].T).view(T, c.n_head, c.head_dim)
-        k = (x @ w[p + "attn_k.weight"].T).view(T, c.n_head_kv, c.head_dim)
-        v = (x @ w[p + "attn_v.weight"].T).view(T, c.n_head_kv, c.head_dim)
+        if c.fused_qkv:   # phi3: one [q | k | v] matrix (llama.cpp/src/models/phi3.cpp)
+            q, k, v = (x @ w[p + "attn_qkv.weight"].T).split([c.q_dim, c.kv_dim, c.kv_dim], dim=-1)
+        else:
+            q, k, v = (x @ w[p + f"attn_{n}.weight"].T for n in "qkv")
+        if c.qkv_bias:    # qwen2 (llama.cpp/src/models/qwen2.cpp)
+            q, k, v = (t + w[p + f"attn_{n}.bias"] for t, n in zip((q, k, v), "qkv"))
+        q = q.reshape(T, c.n_head, c.head_dim)
+        k = k.reshape(T, c.n_head_kv, c.head_dim)
+        v = v.reshape(T, c.n_head_kv, c.head_dim)
+        if c.qk_norm:     # qwen3: RMSNorm over head_dim, before RoPE (llama.cpp/src/models/qwen3.cpp)
+            q = rms_norm(q, w[p + "attn_q_norm.weight"], c.rms_eps)
+            k = rms_norm(k, w[p + "attn_k_norm.weight"], c.rms_eps)
         q = apply_rope(q, pos, self.inv_freq, c.rope_neox)
         k = apply_rope(k, pos, self.inv_freq, c.rope_neox)
         start = cache.length
@@ -111,6 +120,9 @@ class ReferenceModel:
     def ffn(self, il: int, x: torch.Tensor) -> torch.Tensor:
         c, w = self.cfg, self.w
         p = f"blk.{il}."
+        if c.fused_qkv:   # phi3: ffn_up holds [gate | up]; swiglu = silu(first half) * second half
+            g, u = (x @ w[p + "ffn_up.weight"].T).split([c.n_ff, c.n_ff], dim=-1)
+            return (torch.nn.functional.silu(g) * u) @ w[p + "ffn_down.weight"].T
         if not c.is_moe:
             g = x @ w[p + "ffn_gate.weight"].T
             u = x @ w[p + "ffn_up.weight"].T

@@ -26,6 +26,9 @@ class LayerWeights:
     wqkv: DeviceWeight
     wo: DeviceWeight
     ffn_norm: torch.Tensor
+    qkv_bias: torch.Tensor | None = None               # fp32 [local q | k | v rows]  (qwen2)
+    q_norm: torch.Tensor | None = None                 # fp32 [head_dim]              (qwen3)
+    k_norm: torch.Tensor | None = None
     w_gate: DeviceWeight | None = None
     w_up: DeviceWeight | None = None
     w_down: DeviceWeight | None = None
@@ -118,9 +121,17 @@ def load_weights(src: str | GGUFModelFiles, device, layer_range: range | None = 
     layers: dict[int, LayerWeights] = {}
     for il in layer_range:
         p = f"blk.{il}."
-        wq = mat(p + "attn_q.weight", rows=(hq0 * D, hq1 * D))
-        wk = mat(p + "attn_k.weight", rows=(kv_rank * n_kv_local * D, (kv_rank + 1) * n_kv_local * D))
-        wv = mat(p + "attn_v.weight", rows=(kv_rank * n_kv_local * D, (kv_rank + 1) * n_kv_local * D))
+        qr = (hq0 * D, hq1 * D)
+        kr = (kv_rank * n_kv_local * D, (kv_rank + 1) * n_kv_local * D)
+        if cfg.fused_qkv:   # phi3: rows [q | k | v] of one tensor
+            ko, vo = cfg.q_dim, cfg.q_dim + cfg.kv_dim
+            wq = mat(p + "attn_qkv.weight", rows=qr)
+            wk = mat(p + "attn_qkv.weight", rows=(ko + kr[0], ko + kr[1]))
+            wv = mat(p + "attn_qkv.weight", rows=(vo + kr[0], vo + kr[1]))
+        else:
+            wq = mat(p + "attn_q.weight", rows=qr)
+            wk = mat(p + "attn_k.weight", rows=kr)
+            wv = mat(p + "attn_v.weight", rows=kr)
         if wq.wtype == wk.wtype == wv.wtype:
             wqkv = stack_rows([wq, wk, wv])
         else:  # mixed-type files (Q4_K_M stores attn_v at higher precision): decode the odd ones to fp16
@@ -130,8 +141,17 @@ def load_weights(src: str | GGUFModelFiles, device, layer_range: range | None = 
                     else DeviceWeight(GGMLType.F16, dense.shape[0], dense.shape[1], [dense.to(torch.float16).contiguous()]))
         lw = LayerWeights(attn_norm=f32(p + "attn_norm.weight"), wqkv=wqkv,
                           wo=mat(p + "attn_output.weight", cols=(hq0 * D, hq1 * D)), ffn_norm=f32(p + "ffn_norm.weight"))
+        if cfg.qkv_bias:
+            lw.qkv_bias = torch.cat([f32(p + "attn_q.bias")[qr[0]:qr[1]], f32(p + "attn_k.bias")[kr[0]:kr[1]],
+                                     f32(p + "attn_v.bias")[kr[0]:kr[1]]]).contiguous()
+        if cfg.qk_norm:
+            lw.q_norm, lw.k_norm = f32(p + "attn_q_norm.weight"), f32(p + "attn_k_norm.weight")
         f0, f1 = _split(cfg.n_ff, tp_size, tp_rank, 256 if tp_size > 1 else 1)
-        if cfg.is_moe:
+        if cfg.fused_qkv:   # phi3: ffn_up rows [gate | up]
+            lw.w_gate = mat(p + "ffn_up.weight", rows=(f0, f1))
+            lw.w_up = mat(p + "ffn_up.weight", rows=(cfg.n_ff + f0, cfg.n_ff + f1))
+            lw.w_down = mat(p + "ffn_down.weight", cols=(f0, f1))
+        elif cfg.is_moe:
             lw.router = f32(p + "ffn_gate_inp.weight")
             for e in range(cfg.n_expert):
                 lw.e_gate.append(mat(p + "ffn_gate_exps.weight", rows=(f0, f1), sub=e))

@@ -149,8 +149,10 @@ def gemm_f16(w: torch.Tensor, x: torch.Tensor, out: torch.Tensor, epilogue: int 
 # ------------------------------------------------------------------------------------------------
 def rope_kv(qkv: torch.Tensor, pos: torch.Tensor, slot: torch.Tensor, inv_freq: torch.Tensor, k_cache: torch.Tensor,
             v_cache: torch.Tensor, n_head: int, n_head_kv: int, head_dim: int, neox: bool = False,
-            q_out: torch.Tensor | None = None) -> torch.Tensor:
-    """Rotate Q,K; write K,V into the paged cache [pages, Hkv, page, D]; return q (fp16 [T, Hq*D], pre-scaled)."""
+            q_out: torch.Tensor | None = None, bias: torch.Tensor | None = None, q_norm: torch.Tensor | None = None,
+            k_norm: torch.Tensor | None = None, eps: float = 1e-6) -> torch.Tensor:
+    """Rotate Q,K; write K,V into the paged cache [pages, Hkv, page, D]; return q (fp16 [T, Hq*D], pre-scaled).
+    Optional `bias` (qwen2) is added to q|k|v first; `q_norm`/`k_norm` (qwen3) are per-head RMSNorm weights."""
     T = qkv.shape[0]
     page_size = k_cache.shape[2]
     n_rot = inv_freq.numel() * 2
@@ -159,9 +161,16 @@ def rope_kv(qkv: torch.Tensor, pos: torch.Tensor, slot: torch.Tensor, inv_freq: 
         q_out = torch.empty(T, n_head * head_dim, dtype=torch.float16, device=qkv.device)
     if not native(qkv):
         from ..models.reference import apply_rope
-        x = qkv.float().view(T, n_head + 2 * n_head_kv, head_dim)
-        q = apply_rope(x[:, :n_head], pos, inv_freq, neox)
-        k = apply_rope(x[:, n_head:n_head + n_head_kv], pos, inv_freq, neox)
+        x = qkv.float()
+        if bias is not None:
+            x = x + bias
+        x = x.view(T, n_head + 2 * n_head_kv, head_dim)
+        xq, xk = x[:, :n_head], x[:, n_head:n_head + n_head_kv]
+        if q_norm is not None:
+            from ..models.reference import rms_norm
+            xq, xk = rms_norm(xq, q_norm, eps), rms_norm(xk, k_norm, eps)
+        q = apply_rope(xq, pos, inv_freq, neox)
+        k = apply_rope(xk, pos, inv_freq, neox)
         v = x[:, n_head + n_head_kv:]
         q_out.copy_((q * q_scale).reshape(T, -1).to(torch.float16))
         ok = slot >= 0
@@ -169,6 +178,14 @@ def rope_kv(qkv: torch.Tensor, pos: torch.Tensor, slot: torch.Tensor, inv_freq: 
         off = (slot[ok] % page_size).long()
         k_cache[pg, :, off] = k[ok].to(k_cache.dtype)
         v_cache[pg, :, off] = v[ok].to(v_cache.dtype)
+        return q_out
+    if bias is not None or q_norm is not None:
+        _lib.check(_lib.load().dlp_rope_kv_ex(
+            qkv.data_ptr(), int(qkv.dtype == torch.float16), pos.data_ptr(), slot.data_ptr(), inv_freq.data_ptr(),
+            q_out.data_ptr(), k_cache.data_ptr(), v_cache.data_ptr(), T, n_head, n_head_kv, head_dim, n_rot, page_size,
+            int(neox), q_scale, bias.data_ptr() if bias is not None else None, q_norm.data_ptr() if q_norm is not None else None,
+            k_norm.data_ptr() if k_norm is not None else None, float(eps), _stream()), "rope_kv_ex")
+        _count()
         return q_out
     _lib.check(_lib.load().dlp_rope_kv(qkv.data_ptr(), int(qkv.dtype == torch.float16), pos.data_ptr(), slot.data_ptr(),
                                        inv_freq.data_ptr(), q_out.data_ptr(), k_cache.data_ptr(), v_cache.data_ptr(), T,

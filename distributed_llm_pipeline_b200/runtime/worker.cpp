@@ -361,6 +361,7 @@ struct Stage {
     void load(const std::string& path, int a, int b, int n_ctx) {
         g.open(path);
         const std::string ar = g.str.count("general.architecture") ? g.str["general.architecture"] : "llama";
+        if (ar != "llama") throw std::runtime_error("the CPU worker runs llama-architecture checkpoints only (got " + ar + "); use the GPU engine");
         auto N = [&](const char* k, double d) { return g.n(ar + "." + k, d); };
         hp.n_embd = (int)N("embedding_length", 0); hp.n_layer = (int)N("block_count", 0);
         hp.n_head = (int)N("attention.head_count", 0); hp.n_head_kv = (int)N("attention.head_count_kv", hp.n_head);

@@ -78,6 +78,13 @@ int dlp_rmsnorm(float* h, const float* delta, const float* w, void* out_f16, int
 int dlp_rope_kv(const void* qkv, int qkv_is_f16, const int32_t* pos, const int32_t* slot, const float* inv_freq,
                 void* q_out, void* k_cache, void* v_cache, int T, int Hq, int Hkv, int D, int n_rot, int page_size,
                 int neox, float q_scale, void* stream);
+/* Same, for the other architecture families: `bias` [(Hq+2Hkv)*D] fp32 is added to q|k|v first (qwen2,
+ * llama.cpp/src/models/qwen2.cpp), `q_norm`/`k_norm` [D] fp32 are per-head RMSNorm weights applied before the rotation
+ * (qwen3, llama.cpp/src/models/qwen3.cpp).  Any of them may be NULL (q_norm/k_norm only as a pair). */
+int dlp_rope_kv_ex(const void* qkv, int qkv_is_f16, const int32_t* pos, const int32_t* slot, const float* inv_freq,
+                   void* q_out, void* k_cache, void* v_cache, int T, int Hq, int Hkv, int D, int n_rot, int page_size,
+                   int neox, float q_scale, const float* bias, const float* q_norm, const float* k_norm, float eps,
+                   void* stream);
 
 int dlp_swiglu(const void* gate_up, int is_f16, void* out_f16, int T, int F, int ld_in, void* stream);
 

@@ -159,6 +159,39 @@ def test_rope_kv_write(neox, D):
     assert nmse(x[:, Hq + Hkv:].cpu(), vc.cpu()[pg, :, off]) < 1e-6
 
 
+@pytest.mark.parametrize("in_dtype", [torch.float32, torch.float16])
+@pytest.mark.parametrize("D,with_bias,with_norm", [(64, True, False), (128, False, True), (64, True, True), (128, True, True)])
+def test_rope_kv_bias_and_head_norm(D, with_bias, with_norm, in_dtype):
+    """qwen2 bias / qwen3 per-head Q,K RMSNorm fused into the RoPE + KV-write launch, against the fp32 formula."""
+    from distributed_llm_pipeline_b200.models.reference import rms_norm
+    T, Hq, Hkv, page, eps = 7, 6, 2, 16, 1e-6
+    H = Hq + 2 * Hkv
+    qkv = torch.randn(T, H * D, device=DEV).to(in_dtype)
+    pos = torch.arange(3, 3 + T, dtype=torch.int32, device=DEV)
+    slot = (pos + 2 * page).to(torch.int32)
+    inv = (10000.0 ** (-torch.arange(0, D // 2).double() * 2 / D)).float().to(DEV)
+    kc = torch.zeros(4, Hkv, page, D, dtype=torch.float16, device=DEV)
+    vc = torch.zeros_like(kc)
+    bias = torch.randn(H * D, device=DEV) * 0.3 if with_bias else None
+    qn = 1 + 0.2 * torch.randn(D, device=DEV) if with_norm else None
+    kn = 1 + 0.2 * torch.randn(D, device=DEV) if with_norm else None
+    q = ops.rope_kv(qkv, pos, slot, inv, kc, vc, Hq, Hkv, D, True, bias=bias, q_norm=qn, k_norm=kn, eps=eps)
+    x = qkv.float().cpu()
+    if with_bias:
+        x = x + bias.cpu()
+    x = x.view(T, H, D)
+    xq, xk = x[:, :Hq], x[:, Hq:Hq + Hkv]
+    if with_norm:
+        xq, xk = rms_norm(xq, qn.cpu(), eps), rms_norm(xk, kn.cpu(), eps)
+    q_ref = apply_rope(xq, pos.cpu(), inv.cpu(), True) / math.sqrt(D)
+    k_ref = apply_rope(xk, pos.cpu(), inv.cpu(), True)
+    tol = 1e-6 if in_dtype == torch.float32 else 2e-6
+    assert nmse(q_ref.reshape(T, -1), q) < tol
+    pg, off = (slot.cpu() // page).long(), (slot.cpu() % page).long()
+    assert nmse(k_ref, kc.cpu()[pg, :, off]) < tol
+    assert nmse(x[:, Hq + Hkv:], vc.cpu()[pg, :, off]) < tol
+
+
 def _fill_cache(n_pages, Hkv, page, D, seed=0):
     g = torch.Generator(device=DEV).manual_seed(seed)
     kc = torch.randn(n_pages, Hkv, page, D, device=DEV, generator=g).half()

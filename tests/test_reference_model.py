@@ -58,3 +58,30 @@ def test_rope_modes():
     d1 = (apply_rope(q, torch.tensor([3]), inv, False) * apply_rope(k, torch.tensor([7]), inv, False)).sum()
     d2 = (apply_rope(q, torch.tensor([10]), inv, False) * apply_rope(k, torch.tensor([14]), inv, False)).sum()
     assert torch.allclose(d1, d2, atol=1e-4)
+
+
+@pytest.mark.parametrize("key", [("tiny-qwen2", "F16"), ("tiny-qwen2", "Q8_0"), ("tiny-qwen3", "F16"), ("tiny-phi3", "F16"),
+                                 ("tiny-phi3", "Q8_0")])
+def test_other_architectures_match_oracle_cpu(tmp_models, key):
+    """qwen2 (QKV bias), qwen3 (per-head Q/K norm) and phi3 (fused QKV / gate-up tensors), all with half-split RoPE:
+    engine (CPU op fallbacks, paged KV) against the fp32 oracle."""
+    from distributed_llm_pipeline_b200.models.llama import LlamaEngine
+    from distributed_llm_pipeline_b200.models.weights import load_weights
+    path = tmp_models[key]
+    ref = ReferenceModel.from_gguf(path)
+    assert ref.cfg.arch == key[0].split("-")[1] and ref.cfg.rope_neox
+    prompt = list(range(5, 22))
+    toks, ref_logits = ref.generate_greedy(prompt, 4)
+    eng = LlamaEngine(load_weights(path, "cpu"), n_ctx=64, max_seqs=2, page_size=16, max_batch_tokens=32)
+    sid = eng.alloc_seq()
+    lg = eng.prefill(sid, prompt)
+    assert nmse(ref_logits[0], lg.float().flatten()) < 1e-5
+    for i, t in enumerate(toks[:-1]):
+        lg = eng.decode([sid], [t], sample=False)[0]
+        assert nmse(ref_logits[i + 1], lg.float()) < 1e-5
+
+
+def test_unknown_architecture_is_rejected():
+    from distributed_llm_pipeline_b200.models.config import config_from_gguf
+    with pytest.raises(NotImplementedError):
+        config_from_gguf({"general.architecture": "gpt2"})
