@@ -411,9 +411,11 @@ class LlamaEngine:
 
     # ---- public: prefill ------------------------------------------------------------------------
     @torch.no_grad()
-    def prefill(self, sid: int, tokens, hidden_in: torch.Tensor | None = None, chunk: int | None = None):
+    def prefill(self, sid: int, tokens, hidden_in: torch.Tensor | None = None, chunk: int | None = None,
+                all_logits: bool = False):
         """Append `tokens` to sequence `sid`.  Returns logits [vocab] of the last token (last stage) or the
-        hidden states [T, E] to hand to the next pipeline stage."""
+        hidden states [T, E] to hand to the next pipeline stage.  `all_logits=True` (single chunk, tp == 1 or the
+        NCCL TP path) returns logits [T, vocab] for every appended token (speculative verification, perplexity)."""
         seq = self.seqs[sid]
         tokens = torch.as_tensor(tokens, dtype=torch.int32)
         n = tokens.numel()
@@ -446,8 +448,53 @@ class LlamaEngine:
         if not self.last_stage:
             return torch.cat(outs, 0)
         if sp:
+            if all_logits:
+                raise NotImplementedError("all_logits is not available on the sequence-parallel prefill path")
             return sp_logits[0]
+        if all_logits:
+            if n > chunk:
+                raise ValueError("all_logits needs the tokens to fit one chunk")
+            xn = ops.rmsnorm(self.h[:T], self.w.out_norm, self.cfg.rms_eps)
+            lg = ops.linear(self.w.lm_head, xn, "f32", scratch=self._scratch_for(self.w.lm_head))
+            return self.comm.allgather_logits(lg, self.w.vocab_range, self.cfg.vocab_size)
         return self._head(slice(T - 1, T), 1)[0]
+
+    @torch.no_grad()
+    def embed(self, tokens, pooling: str = "mean", normalize: bool = True) -> torch.Tensor:
+        """Sentence embedding of `tokens`: final-norm hidden states pooled over the sequence (`mean` | `last` | `cls` |
+        `none` -> [T, E]) and L2-normalised.  Parity: `llama_get_embeddings_seq` with `--pooling`
+        (`llama.cpp/src/llama-context.cpp` embeddings output, `examples/embedding`); runs in a scratch sequence slot."""
+        if self.fused_tp or not (self.first_stage and self.last_stage):
+            raise NotImplementedError("embed() runs on a single-stage engine (tp == 1 or the NCCL TP path)")
+        tokens = list(tokens)
+        if len(tokens) > self.max_tokens:
+            raise ValueError(f"{len(tokens)} tokens exceed the batch limit {self.max_tokens}")
+        sid = self.alloc_seq()
+        try:
+            seq = self.seqs[sid]
+            T = len(tokens)
+            self.kv.ensure(seq, T)
+            pos = torch.arange(T, dtype=torch.int32)
+            pages = torch.tensor(seq.pages, dtype=torch.int32)
+            self.pos[:T].copy_(pos)
+            self.slot[:T].copy_((pages[(pos // self.page_size).long()] * self.page_size + pos % self.page_size).to(torch.int32))
+            self.tokens[:T].copy_(torch.as_tensor(tokens, dtype=torch.int32))
+            self._embed(T)
+            self._run_layers(T, self._attn_prefill_for(sid, 0))
+            xn = ops.rmsnorm(self.h[:T], self.w.out_norm, self.cfg.rms_eps).float()
+        finally:
+            self.free_seq(sid)
+        if pooling == "mean":
+            e = xn.mean(0)
+        elif pooling == "last":
+            e = xn[-1]
+        elif pooling == "cls":
+            e = xn[0]
+        elif pooling == "none":
+            e = xn
+        else:
+            raise ValueError(f"unknown pooling {pooling!r}")
+        return torch.nn.functional.normalize(e, dim=-1) if normalize else e
 
     # ---- public: decode -------------------------------------------------------------------------
     def _decode_body(self, B: int, sample: bool):

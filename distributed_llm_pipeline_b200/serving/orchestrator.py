@@ -139,6 +139,20 @@ class Orchestrator:
             if method == "POST" and path == "/detokenize":
                 await self._json(writer, {"content": self.sched.tok.decode(json.loads(body or b"{}").get("tokens", []), False)})
                 return True
+            if method == "POST" and path in ("/embedding", "/embeddings", "/v1/embeddings"):
+                d = json.loads(body or b"{}")
+                inp = d.get("input", d.get("content", ""))
+                items = inp if isinstance(inp, list) and (not inp or not isinstance(inp[0], int)) else [inp]
+                loop = asyncio.get_running_loop()
+                pooling = str(d.get("pooling", "mean"))
+                vecs = [await loop.run_in_executor(None, self.sched.embed, it, pooling) for it in items]
+                if path.startswith("/v1"):
+                    await self._json(writer, {"object": "list", "model": self.info.get("name", "model"),
+                                              "data": [{"object": "embedding", "index": i, "embedding": v} for i, v in enumerate(vecs)]})
+                else:
+                    await self._json(writer, [{"index": i, "embedding": v} for i, v in enumerate(vecs)] if isinstance(inp, list) and items is inp
+                                     else {"embedding": vecs[0]})
+                return True
             if method == "GET" and path == "/health":
                 await self._json(writer, {"status": "ok"})
                 return True
@@ -236,7 +250,20 @@ class Orchestrator:
 
     # ---- llama-server style / OpenAI style completions -----------------------------------------------------------
     def _sampling_from(self, d: dict) -> SamplingParams:
-        return SamplingParams(temperature=float(d.get("temperature", 0.8)), top_k=int(d.get("top_k", 40)), top_p=float(d.get("top_p", 0.95)),
+        schema = d.get("json_schema")
+        rf = d.get("response_format") or {}
+        if schema is None and rf.get("type") == "json_object":
+            schema = rf.get("schema") or {}
+        if schema is None and rf.get("type") == "json_schema":
+            schema = (rf.get("json_schema") or {}).get("schema") or {}
+        return SamplingParams(grammar=str(d.get("grammar", "") or ""), json_schema=schema,
+                              top_n_sigma=float(d.get("top_n_sigma", -1.0)), dynatemp_range=float(d.get("dynatemp_range", 0.0)),
+                              dynatemp_exponent=float(d.get("dynatemp_exponent", 1.0)), xtc_probability=float(d.get("xtc_probability", 0.0)),
+                              xtc_threshold=float(d.get("xtc_threshold", 0.1)), mirostat=int(d.get("mirostat", 0)),
+                              mirostat_tau=float(d.get("mirostat_tau", 5.0)), mirostat_eta=float(d.get("mirostat_eta", 0.1)),
+                              logit_bias={int(k): float(v) for k, v in (d.get("logit_bias") or {}).items()} if isinstance(d.get("logit_bias"), dict)
+                              else {int(k): float(v) for k, v in (d.get("logit_bias") or [])},
+                              temperature=float(d.get("temperature", 0.8)), top_k=int(d.get("top_k", 40)), top_p=float(d.get("top_p", 0.95)),
                               min_p=float(d.get("min_p", 0.05)), typical_p=float(d.get("typical_p", 1.0)),
                               repeat_penalty=float(d.get("repeat_penalty", 1.0)), frequency_penalty=float(d.get("frequency_penalty", 0.0)),
                               presence_penalty=float(d.get("presence_penalty", 0.0)), seed=int(d.get("seed", 0) if d.get("seed", 0) >= 0 else 0))
@@ -330,7 +357,7 @@ def build_service(model: str, device: str = "cuda", n_ctx: int = 2048, n_slots: 
     f = open_gguf(model)
     t0 = time.time()
     w = load_weights(f, dev)
-    eng = LlamaEngine(w, n_ctx=n_ctx, max_seqs=n_slots, page_size=page_size if dev != "cpu" else 16, max_batch_tokens=n_batch)
+    eng = LlamaEngine(w, n_ctx=n_ctx, max_seqs=n_slots + 1, page_size=page_size if dev != "cpu" else 16, max_batch_tokens=n_batch)
     tok = Tokenizer(f.metadata)
     cfg = w.cfg
     logs = [
@@ -340,7 +367,7 @@ def build_service(model: str, device: str = "cuda", n_ctx: int = 2048, n_slots: 
     ]
     info = {"name": str(f.metadata.get("general.name", os.path.basename(model))), "n_params": cfg.n_params(), "n_ctx_train": cfg.n_ctx_train,
             "metadata": {"tokenizer.chat_template": f.metadata.get("tokenizer.chat_template", "")}}
-    sched = Scheduler(eng, tok, n_batch=n_batch)
+    sched = Scheduler(eng, tok, n_batch=n_batch, n_slots=n_slots)
     return sched, info, logs
 
 

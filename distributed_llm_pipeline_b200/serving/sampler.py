@@ -3,7 +3,8 @@
 Parity: default chain order of the reference (`llama.cpp/common/common.h:201-210`, `common/sampling.cpp:179-311`):
 penalties -> top-k -> top-p -> min-p -> temperature -> dist.  Implemented samplers: repetition/frequency/presence
 penalties (`llama-sampling.cpp:2777`), top-k (`:1348`), top-p (`:1543`), min-p (`:1704`), typical (`:1814`),
-temperature (`:1918`), greedy (`:1011`), seeded multinomial (`:1255`), logit bias (`:3455`).
+temperature (`:1918`), dynamic temperature (`temp_ext :2115`), XTC (`:2222`), mirostat v2 (`:2445`), top-n-sigma (`:2876`),
+grammar (`:2625`, see grammar.py), greedy (`:1011`), seeded multinomial (`:1255`), logit bias (`:3455`).
 """
 from __future__ import annotations
 
@@ -25,6 +26,23 @@ class SamplingParams:
     repeat_last_n: int = 64
     seed: int = 0
     logit_bias: dict[int, float] = field(default_factory=dict)
+    top_n_sigma: float = -1.0          # keep logits within n standard deviations of the maximum (<= 0: off)
+    dynatemp_range: float = 0.0        # entropy-scaled temperature in [temp - range, temp + range]
+    dynatemp_exponent: float = 1.0
+    xtc_probability: float = 0.0       # "exclude top choices": with this probability drop all but the least likely
+    xtc_threshold: float = 0.1         # candidate whose probability is >= threshold
+    mirostat: int = 0                  # 2 = mirostat v2 (replaces top-k/top-p/min-p)
+    mirostat_tau: float = 5.0
+    mirostat_eta: float = 0.1
+    grammar: str = ""                  # GBNF text; "" = unconstrained
+    json_schema: dict | None = None    # converted to GBNF when `grammar` is empty
+
+    @property
+    def host_only(self) -> bool:
+        """True when the chain needs a sampler the device kernel does not implement."""
+        return bool(self.repeat_penalty != 1.0 or self.frequency_penalty or self.presence_penalty or self.logit_bias
+                    or self.typical_p < 1.0 or self.top_n_sigma > 0 or self.dynatemp_range > 0 or self.xtc_probability > 0
+                    or self.mirostat or self.grammar or self.json_schema is not None)
 
     @property
     def greedy(self) -> bool:
@@ -89,13 +107,63 @@ def sample_reference(logits: torch.Tensor, top_k: int, top_p: float, min_p: floa
 class Sampler:
     """Stateful per-request sampler (history for penalties, private RNG stream)."""
 
-    def __init__(self, params: SamplingParams):
+    def __init__(self, params: SamplingParams, tokenizer=None):
         self.p = params
         self.history: list[int] = []
         self.gen = torch.Generator().manual_seed(params.seed)
+        self.mu = 2.0 * params.mirostat_tau
+        self.constraint = None
+        gtext = params.grammar
+        if not gtext and params.json_schema is not None:
+            from .grammar import json_schema_to_gbnf
+            gtext = json_schema_to_gbnf(params.json_schema)
+        if gtext:
+            if tokenizer is None:
+                raise ValueError("grammar-constrained sampling needs the tokenizer")
+            from .grammar import GrammarConstraint
+            self.constraint = GrammarConstraint(gtext, tokenizer.token_texts(), tuple(tokenizer.stop_ids))
 
     def accept(self, token: int):
         self.history.append(token)
+        if self.constraint is not None:
+            self.constraint.accept(token)
+
+    def _pick(self, row: torch.Tensor) -> int:
+        p = self.p
+        if p.greedy:
+            return int(row.argmax())
+        if p.top_n_sigma > 0:
+            row = row.masked_fill(row < row.max() - p.top_n_sigma * row.std(), float("-inf"))
+        if p.mirostat == 2:
+            probs = torch.softmax(row / p.temperature, -1)
+            surprise = -torch.log2(probs.clamp_min(1e-30))
+            keep = surprise <= self.mu
+            if not bool(keep.any()):
+                keep = surprise == surprise.min()
+            probs = torch.where(keep, probs, torch.zeros_like(probs))
+            probs = probs / probs.sum()
+            tok = int(torch.multinomial(probs, 1, generator=self.gen))
+            self.mu -= p.mirostat_eta * (float(-torch.log2(probs[tok])) - p.mirostat_tau)
+            return tok
+        vals, ids = filter_candidates(row, p.top_k, p.top_p, p.min_p, p.typical_p)
+        ok = torch.isfinite(vals)
+        vals, ids = vals[ok], ids[ok]
+        temp = p.temperature
+        if p.dynatemp_range > 0 and vals.numel() > 1:
+            pr = torch.softmax(vals, -1)
+            ent = float(-(pr * torch.log(pr.clamp_min(1e-30))).sum())
+            max_ent = float(torch.log(torch.tensor(float(vals.numel()))))
+            lo, hi = max(0.0, temp - p.dynatemp_range), temp + p.dynatemp_range
+            temp = lo + (hi - lo) * (ent / max_ent) ** p.dynatemp_exponent
+        probs = torch.softmax(vals / max(temp, 1e-6), -1)
+        if p.xtc_probability > 0 and float(torch.rand(1, generator=self.gen)) < p.xtc_probability:
+            above = (probs >= p.xtc_threshold).nonzero().flatten()
+            if above.numel() >= 2:                         # candidates are sorted: drop all but the last one above
+                keep = torch.ones_like(probs, dtype=torch.bool)
+                keep[above[:-1]] = False
+                probs = torch.where(keep, probs, torch.zeros_like(probs))
+                probs = probs / probs.sum()
+        return int(ids[torch.multinomial(probs, 1, generator=self.gen)])
 
     def sample(self, logits: torch.Tensor) -> int:
         p = self.p
@@ -103,11 +171,13 @@ class Sampler:
         for tid, bias in p.logit_bias.items():
             row[tid] += bias
         row = apply_penalties(row, self.history, p)
-        if p.greedy:
-            tok = int(row.argmax())
-        else:
-            vals, ids = filter_candidates(row, p.top_k, p.top_p, p.min_p, p.typical_p)
-            probs = torch.softmax(vals / p.temperature, -1)
-            tok = int(ids[torch.multinomial(probs, 1, generator=self.gen)])
+        tok = self._pick(row)
+        if self.constraint is not None and not self.constraint.allowed(tok):
+            # the unconstrained pick breaks the grammar: mask the whole vocabulary and pick again (the reference checks
+            # the sampled token first for the same reason: the full mask is the expensive part)
+            allowed = torch.tensor(self.constraint.mask(), dtype=torch.bool)
+            if not bool(allowed.any()):
+                raise RuntimeError("grammar: no token can continue the output")
+            tok = self._pick(row.masked_fill(~allowed, float("-inf")))
         self.accept(tok)
         return tok

@@ -128,9 +128,10 @@ class Metrics:
 class Scheduler:
     """Owns the engine; `step()` advances every active slot by one scheduling quantum."""
 
-    def __init__(self, engine, tokenizer: Tokenizer, n_batch: int | None = None, log: Callable[[str], None] | None = None):
+    def __init__(self, engine, tokenizer: Tokenizer, n_batch: int | None = None, log: Callable[[str], None] | None = None,
+                 n_slots: int | None = None):
         self.eng, self.tok = engine, tokenizer
-        self.n_slots = engine.max_seqs
+        self.n_slots = min(n_slots or engine.max_seqs, engine.max_seqs)
         self.n_batch = min(n_batch or engine.max_tokens, engine.max_tokens)
         self.slots = [Slot(i) for i in range(self.n_slots)]
         self.queue: deque[Request] = deque()
@@ -141,6 +142,7 @@ class Scheduler:
         self._ids = itertools.count(1)
         self._stop = False
         self._thread: threading.Thread | None = None
+        self._jobs: list = []
         self.log = log or (lambda s: None)
 
     # ---- submission -------------------------------------------------------------------------------
@@ -196,7 +198,7 @@ class Scheduler:
         slot.cache_tokens = slot.cache_tokens[:keep]
         slot.n_past = keep
         slot.req, slot.state = req, SlotState.PROMPT
-        slot.sampler = Sampler(req.sampling)
+        slot.sampler = Sampler(req.sampling, self.tok)
         slot.decoder = StreamDecoder(self.tok)
         req.n_prompt_cached = keep
         req.t_start = time.time()
@@ -214,6 +216,14 @@ class Scheduler:
     @torch.no_grad()
     def step(self) -> bool:
         """Returns False when there was nothing to do."""
+        with self.lock:
+            jobs, self._jobs = self._jobs, []
+        for fn, fut in jobs:            # engine-side calls from other threads (embeddings), between batches
+            try:
+                fut["value"] = fn(self.eng)
+            except Exception as e:       # noqa: BLE001 - handed back to the caller
+                fut["error"] = e
+            fut["done"].set()
         with self.lock:
             while self.queue:
                 slot = self._pick_slot(self.queue[0])
@@ -296,8 +306,7 @@ class Scheduler:
 
     def _device_samplable(self, s: Slot) -> bool:
         p = s.req.sampling
-        return (p.repeat_penalty == 1.0 and p.frequency_penalty == 0.0 and p.presence_penalty == 0.0 and not p.logit_bias
-                and p.typical_p >= 1.0 and self.eng.device.type == "cuda")
+        return not p.host_only and self.eng.device.type == "cuda"
 
     @staticmethod
     def _same_params(slots: list[Slot]) -> bool:
@@ -388,7 +397,7 @@ class Scheduler:
         while not self._stop:
             if not self.step():
                 with self.wake:
-                    if not self.queue and not self._stop:
+                    if not self.queue and not self._jobs and not self._stop:
                         self.wake.wait(timeout=0.05)
 
     # ---- blocking convenience ------------------------------------------------------------------------------
@@ -400,6 +409,37 @@ class Scheduler:
         else:
             req.done.wait()
         return req
+
+    def run_on_engine(self, fn, timeout: float = 120.0):
+        """Run `fn(engine)` on the scheduler thread (the only thread that touches the engine) and return its value."""
+        fut = {"done": threading.Event()}
+        with self.wake:
+            self._jobs.append((fn, fut))
+            self.wake.notify()
+        if self._thread is None:
+            self.step()
+        if not fut["done"].wait(timeout):
+            raise TimeoutError("engine job timed out")
+        if "error" in fut:
+            raise fut["error"]
+        return fut["value"]
+
+    def embed(self, text_or_ids, pooling: str = "mean", normalize: bool = True) -> list[float]:
+        """Pooled sentence embedding through the engine (llama-server `/embedding`, `server-context.cpp` embedding
+        tasks).  Needs one engine sequence slot beyond the serving slots (build_service reserves it)."""
+        ids = self.tok.encode(text_or_ids) if isinstance(text_or_ids, str) else list(text_or_ids)
+        ids = ids[: self.eng.max_tokens]
+        self.metrics.add(prompt_tokens_total=len(ids))
+
+        def job(eng):
+            if not eng._free_sids:       # every engine sequence is parked in a slot: give up one idle slot's cache
+                idle = next((s for s in self.slots if s.state == SlotState.IDLE and s.sid is not None), None)
+                if idle is None:
+                    raise RuntimeError("no free sequence slot for an embedding request")
+                eng.free_seq(idle.sid)
+                idle.sid, idle.cache_tokens, idle.n_past = None, [], 0
+            return eng.embed(ids, pooling, normalize).cpu().tolist()
+        return self.run_on_engine(job)
 
     def slots_info(self) -> list[dict]:
         return [{"id": s.idx, "state": s.state.name.lower(), "n_past": s.n_past, "n_cached": len(s.cache_tokens),

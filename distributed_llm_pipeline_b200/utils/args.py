@@ -53,6 +53,22 @@ SAMPLING = [
     Opt(("--presence-penalty",), "presence penalty", 0.0, float, "DLP_ARG_PRESENCE_PENALTY"),
     Opt(("--frequency-penalty",), "frequency penalty", 0.0, float, "DLP_ARG_FREQUENCY_PENALTY"),
     Opt(("-s", "--seed"), "RNG seed", 0, int, "DLP_ARG_SEED"),
+    Opt(("--top-nsigma",), "top-n-sigma (<= 0: off)", -1.0, float, "DLP_ARG_TOP_NSIGMA"),
+    Opt(("--dynatemp-range",), "dynamic temperature range", 0.0, float, "DLP_ARG_DYNATEMP_RANGE"),
+    Opt(("--dynatemp-exp",), "dynamic temperature exponent", 1.0, float, "DLP_ARG_DYNATEMP_EXP"),
+    Opt(("--xtc-probability",), "XTC probability", 0.0, float, "DLP_ARG_XTC_PROBABILITY"),
+    Opt(("--xtc-threshold",), "XTC threshold", 0.1, float, "DLP_ARG_XTC_THRESHOLD"),
+    Opt(("--mirostat",), "0 = off, 2 = mirostat v2", 0, int, "DLP_ARG_MIROSTAT"),
+    Opt(("--mirostat-ent",), "mirostat target entropy (tau)", 5.0, float, "DLP_ARG_MIROSTAT_ENT"),
+    Opt(("--mirostat-lr",), "mirostat learning rate (eta)", 0.1, float, "DLP_ARG_MIROSTAT_LR"),
+    Opt(("--grammar",), "GBNF grammar text constraining the output", "", str, "DLP_ARG_GRAMMAR"),
+    Opt(("--grammar-file",), "read the GBNF grammar from a file", None, str),
+    Opt(("-j", "--json-schema"), "JSON schema (text) constraining the output", None, str, "DLP_ARG_JSON_SCHEMA"),
+]
+SPECULATIVE = [
+    Opt(("-md", "--model-draft"), "draft GGUF model for speculative decoding (greedy)", None, str, "DLP_ARG_MODEL_DRAFT"),
+    Opt(("--lookup",), "speculative decoding with prompt-lookup (n-gram) drafts", False, None, action="store_true"),
+    Opt(("--draft-max", "--draft"), "tokens to draft per verification pass", 8, int, "DLP_ARG_DRAFT_MAX"),
 ]
 GENERATION = [
     Opt(("-p", "--prompt"), "prompt text", "", str, "DLP_ARG_PROMPT"),
@@ -84,6 +100,12 @@ def build_parser(description: str, groups: list[list[Opt]]) -> argparse.Argument
 
 def sampling_from_args(a):
     from ..serving.sampler import SamplingParams
+    import json
+    grammar = open(a.grammar_file).read() if getattr(a, "grammar_file", None) else getattr(a, "grammar", "")
+    schema = json.loads(a.json_schema) if getattr(a, "json_schema", None) else None
     return SamplingParams(temperature=a.temp, top_k=a.top_k, top_p=a.top_p, min_p=a.min_p, typical_p=a.typical,
                           repeat_penalty=a.repeat_penalty, presence_penalty=a.presence_penalty,
-                          frequency_penalty=a.frequency_penalty, seed=a.seed)
+                          frequency_penalty=a.frequency_penalty, seed=a.seed, top_n_sigma=a.top_nsigma,
+                          dynatemp_range=a.dynatemp_range, dynatemp_exponent=a.dynatemp_exp, xtc_probability=a.xtc_probability,
+                          xtc_threshold=a.xtc_threshold, mirostat=a.mirostat, mirostat_tau=a.mirostat_ent,
+                          mirostat_eta=a.mirostat_lr, grammar=grammar or "", json_schema=schema)

@@ -191,6 +191,22 @@ class Tokenizer:
             return t.replace(SPM_SPACE, " ").encode("utf-8")
         return bytes(self.u2b.get(ch, ord("?")) for ch in t)
 
+    def token_texts(self) -> list[str | None]:
+        """Text of every token for grammar matching: None for control tokens and for byte fragments that are not valid
+        UTF-8 on their own (the grammar sampler never picks those)."""
+        if getattr(self, "_texts", None) is None:
+            out: list[str | None] = []
+            for tid in range(self.n_vocab):
+                if self.types[tid] in (TokenType.CONTROL, TokenType.UNKNOWN, TokenType.UNUSED):
+                    out.append(None)
+                    continue
+                try:
+                    out.append(self.token_bytes(tid).decode("utf-8") or None)
+                except UnicodeDecodeError:
+                    out.append(None)
+            self._texts = out
+        return self._texts
+
     def decode(self, ids: list[int], strip_leading_space: bool = True) -> str:
         data = b"".join(self.token_bytes(i) for i in ids)
         s = data.decode("utf-8", errors="replace")

@@ -57,3 +57,29 @@ def test_batched_decode_matches_single(tmp_models):
         ref.forward(p, cache)
         ref.advance(cache, len(p))
         assert nmse(ref.forward([t], cache)[-1], lg[row]) < 1e-3
+
+
+def test_speculative_verify_and_embed_on_gpu(tmp_models):
+    """Draft-and-verify on the CUDA engine: the T = k+1 verify forward (GEMM path) must reproduce the mat-vec decode
+    path's greedy tokens, except where the oracle's top-2 logits are closer than fp16 noise."""
+    from distributed_llm_pipeline_b200.serving.speculative import ModelDrafter, SpecStats, generate_speculative
+    path = tmp_models[("tiny128", "F16")]
+    mk = lambda: LlamaEngine(load_weights(path, "cuda"), n_ctx=256, max_seqs=2, page_size=16, max_batch_tokens=64)  # noqa: E731
+    eng, draft = mk(), mk()
+    prompt = PROMPT * 2
+    base = eng.generate(prompt, 32)
+    st = SpecStats()
+    out = generate_speculative(eng, prompt, 32, ModelDrafter(draft), 6, stats=st)
+    assert st.tokens_per_pass > 2.0 and len(out) == 32
+    if out != base:
+        i = next(k for k in range(32) if out[k] != base[k])
+        ref = ReferenceModel.from_gguf(path)
+        cache = ref.new_cache(128)
+        lg = ref.forward(prompt + base[:i], cache)[-1]
+        assert abs(float(lg[out[i]] - lg[base[i]])) < 2e-2, (i, out[i], base[i])
+    ids = [1, 5, 9, 200, 33, 7, 8]
+    e = eng.embed(ids, pooling="none", normalize=False)
+    from distributed_llm_pipeline_b200.models.reference import rms_norm
+    ref = ReferenceModel.from_gguf(path)
+    h = ref.forward(ids, ref.new_cache(16), return_hidden=True)
+    assert nmse(rms_norm(h, ref.w["output_norm.weight"], ref.cfg.rms_eps), e) < 1e-4

@@ -157,3 +157,33 @@ def test_stop_string_and_n_predict(server):
         needle = full.text[2:4]
         cut = sched.generate("abc", n_predict=10, sampling=SamplingParams(temperature=0.0), stop=[needle])
         assert needle not in cut.text and cut.finish_reason == "stop"
+
+
+def test_embedding_routes(server):
+    port, sched = server
+    _, _, body = _http(port, "POST", "/embedding", json.dumps({"content": "hello world"}).encode())
+    e = json.loads(body)["embedding"]
+    assert len(e) == sched.eng.cfg.n_embd and abs(sum(x * x for x in e) - 1.0) < 1e-3
+    _, _, body = _http(port, "POST", "/v1/embeddings", json.dumps({"input": ["hello world", "other text"]}).encode())
+    d = json.loads(body)
+    assert d["object"] == "list" and len(d["data"]) == 2
+    a, b = d["data"][0]["embedding"], d["data"][1]["embedding"]
+    assert max(abs(x - y) for x, y in zip(a, e)) < 1e-5 and max(abs(x - y) for x, y in zip(a, b)) > 1e-3
+    # generation still works afterwards (the embedding ran in a scratch sequence between batches)
+    r = sched.generate("abc", n_predict=3, sampling=SamplingParams(temperature=0.0))
+    assert r.finish_reason in ("length", "stop")
+
+
+def test_grammar_constrained_completion(server):
+    port, sched = server
+    gbnf = 'root ::= ("ka" | "ri" | "to")+ "."'
+    _, _, body = _http(port, "POST", "/completion",
+                       json.dumps({"prompt": "say", "n_predict": 12, "temperature": 0.7, "seed": 5, "grammar": gbnf}).encode())
+    text = json.loads(body)["content"]
+    from distributed_llm_pipeline_b200.serving.grammar import Grammar
+    g = Grammar(gbnf)
+    body_txt = text.strip()
+    assert body_txt and (g.matches(body_txt) or all(g.clone().accepts(body_txt[:i]) for i in range(1, len(body_txt) + 1)))
+    assert set(body_txt) <= set("kario.t")
+    r = sched.generate("json:", n_predict=24, sampling=SamplingParams(temperature=0.0, json_schema={"type": "boolean"}))
+    assert r.text.strip() in ("true", "false") and r.finish_reason == "stop"

@@ -11,12 +11,12 @@ import time
 
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 
-from distributed_llm_pipeline_b200.utils.args import COMMON, GENERATION, SAMPLING, build_parser, sampling_from_args  # noqa: E402
+from distributed_llm_pipeline_b200.utils.args import COMMON, GENERATION, SAMPLING, SPECULATIVE, build_parser, sampling_from_args  # noqa: E402
 from distributed_llm_pipeline_b200.utils.log import get_logger  # noqa: E402
 
 
 def main(argv=None):
-    a = build_parser("dlp-cli - generate text from a GGUF model", [COMMON, SAMPLING, GENERATION]).parse_args(argv)
+    a = build_parser("dlp-cli - generate text from a GGUF model", [COMMON, SAMPLING, GENERATION, SPECULATIVE]).parse_args(argv)
     if not a.model:
         sys.exit("dlp-cli: -m model.gguf is required")
     log = get_logger()
@@ -46,8 +46,24 @@ def main(argv=None):
         tok = Tokenizer(f.metadata)
         log.info(f"load_tensors: offloaded {w.cfg.n_layer + 1}/{w.cfg.n_layer + 1} layers to GPU ({dev}), {w.nbytes() / 2**20:.1f} MiB")
     log.info(f"model loaded in {time.time() - t0:.2f} s | n_ctx {a.ctx_size} | slots {a.parallel}")
-    sched = Scheduler(eng, tok, n_batch=a.batch_size)
     prompt = open(a.file).read() if a.file else a.prompt
+    if (a.model_draft or a.lookup) and not a.rpc:
+        # draft-and-verify generation (llama-speculative / llama-lookup): greedy, single sequence
+        from distributed_llm_pipeline_b200.serving.speculative import ModelDrafter, NgramDrafter, SpecStats, generate_speculative
+        if a.model_draft:
+            dw = load_weights(a.model_draft, dev)
+            drafter = ModelDrafter(LlamaEngine(dw, n_ctx=a.ctx_size, max_seqs=1, page_size=eng.page_size, max_batch_tokens=eng.max_tokens))
+        else:
+            drafter = NgramDrafter()
+        st = SpecStats()
+        t1 = time.time()
+        ids = generate_speculative(eng, tok.encode(prompt), a.predict, drafter, a.draft_max, () if a.ignore_eos else tuple(tok.stop_ids), st)
+        sys.stdout.write(tok.decode(ids) + "\n")
+        log.info(f"speculative: {st.n_generated} tokens in {st.n_target_passes} target passes ({st.tokens_per_pass:.2f} tok/pass), "
+                 f"drafted {st.n_drafted}, accepted {st.n_accepted} ({100 * st.acceptance:.1f}%), {st.n_generated / (time.time() - t1):.1f} tok/s")
+        log.flush()
+        return
+    sched = Scheduler(eng, tok, n_batch=a.batch_size)
 
     def on_event(kind, content):
         if kind == "token":
