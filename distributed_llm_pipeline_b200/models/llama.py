@@ -175,6 +175,49 @@ class LlamaEngine:
         seq.length = new_len
         self.seq_len_dev[sid] = new_len
 
+    def copy_seq(self, src: int, dst: int, n: int | None = None):
+        """Copy the first `n` cached tokens (default: all) of sequence `src` into `dst` (which is overwritten).
+        Parity: `llama_memory_seq_cp` (`llama-kv-cache.cpp:322-392`) - used for prompt sharing between slots / beams."""
+        s, d = self.seqs[src], self.seqs[dst]
+        n = s.length if n is None else min(n, s.length)
+        self.truncate_seq(dst, 0)
+        self.kv.ensure(d, n)
+        npg = (n + self.page_size - 1) // self.page_size
+        if npg:
+            sp = torch.tensor(s.pages[:npg], dtype=torch.long, device=self.device)
+            dp = torch.tensor(d.pages[:npg], dtype=torch.long, device=self.device)
+            for il in self.w.layer_range:
+                self.kv.k[il][dp] = self.kv.k[il][sp]
+                self.kv.v[il][dp] = self.kv.v[il][sp]
+        d.length = n
+        self.seq_len_dev[dst] = n
+
+    def shift_seq(self, sid: int, n_keep: int, n_discard: int):
+        """Context shift: drop cached tokens [n_keep, n_keep + n_discard) and slide the rest down, re-rotating their keys by
+        -n_discard positions so that attention sees contiguous positions again.  Parity: `llama_memory_seq_rm` +
+        `llama_memory_seq_add(-n_discard)` and the K-shift graph (`llama-kv-cache.cpp:1379-1484`), as driven by the server's
+        context shift (`server-context.cpp:1944-2003`).  Rare, latency-insensitive: gathers / scatters pages with torch ops."""
+        from .reference import apply_rope
+        seq = self.seqs[sid]
+        n, ps = seq.length, self.page_size
+        n_keep = max(0, min(n_keep, n))
+        n_discard = max(0, min(n_discard, n - n_keep))
+        if n_discard == 0:
+            return
+        pages = torch.tensor(seq.pages[: (n + ps - 1) // ps], dtype=torch.long, device=self.device)
+        tail = n - n_keep - n_discard
+        delta = torch.full((tail,), -n_discard, dtype=torch.int32, device=self.device)
+        for il in self.w.layer_range:
+            for which, cache in (("k", self.kv.k[il]), ("v", self.kv.v[il])):
+                flat = cache[pages].permute(0, 2, 1, 3).reshape(-1, self.Hkv, self.D)          # [tokens, Hkv, D]
+                moved = flat[n_keep + n_discard:n].clone()
+                if which == "k" and tail:
+                    # R(p - d) k = R(-d) R(p) k: rotate the stored (already rotated) keys by the position delta
+                    moved = apply_rope(moved.float(), delta, self.inv_freq, self.cfg.rope_neox).to(flat.dtype)
+                flat[n_keep:n_keep + tail] = moved
+                cache[pages] = flat.view(len(pages), ps, self.Hkv, self.D).permute(0, 2, 1, 3)
+        self.truncate_seq(sid, n_keep + tail)
+
     def _scratch_for(self, *ws):
         if not ops.TWO_PASS_DEQUANT:   # block-quant decode is fused into the GEMM: no scratch
             return None

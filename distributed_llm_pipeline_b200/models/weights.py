@@ -79,9 +79,51 @@ def _split(n: int, parts: int, rank: int, align: int = 1) -> tuple[int, int]:
     return rank * per, (rank + 1) * per
 
 
+class LoraAdapter:
+    """A GGUF LoRA adapter (`general.type = adapter`, `adapter.type = lora`, `adapter.lora.alpha`, tensor pairs
+    `<base tensor>.lora_a` [r, in] / `.lora_b` [out, r]) as written by the reference's `convert_lora_to_gguf.py` and read by
+    `llama_adapter_lora_init` (`llama.cpp/src/llama-adapter.cpp`).  The reference keeps adapters separate and adds
+    `scale * B(A x)` per mat-mul (`build_lora_mm`); this engine folds `W += scale * alpha / r * B @ A` into the weights at
+    load time (decode streams the merged fp16 matrix once; no extra launches)."""
+
+    def __init__(self, path: str, scale: float = 1.0):
+        self.f = open_gguf(path)
+        md = self.f.metadata
+        if md.get("general.type", "adapter") != "adapter" or md.get("adapter.type", "lora") != "lora":
+            raise ValueError(f"{path}: not a LoRA adapter GGUF")
+        self.alpha = float(md.get("adapter.lora.alpha", 0.0))
+        self.scale = scale
+        self.targets = {n[: -len(".lora_a")] for n in self.f.tensors if n.endswith(".lora_a")}
+
+    def delta(self, name: str) -> np.ndarray | None:
+        if name not in self.targets:
+            return None
+        a = np.asarray(self.f.array(name + ".lora_a"), dtype=np.float32)      # [r, in]
+        b = np.asarray(self.f.array(name + ".lora_b"), dtype=np.float32)      # [out, r]
+        r = a.shape[0]
+        return (self.scale * (self.alpha / r if self.alpha else 1.0)) * (b @ a)
+
+
+def write_lora_gguf(path: str, deltas: dict[str, tuple[np.ndarray, np.ndarray]], alpha: float, arch: str = "llama") -> str:
+    """Write a LoRA adapter file ({tensor name: (A [r, in], B [out, r])}) - the test / tooling counterpart of the loader."""
+    from ..gguf import GGUFWriter
+    w = GGUFWriter(path)
+    w.add("general.architecture", arch)
+    w.add("general.type", "adapter")
+    w.add("adapter.type", "lora")
+    w.add("adapter.lora.alpha", float(alpha))
+    for name, (a, b) in deltas.items():
+        for suffix, m in ((".lora_a", a), (".lora_b", b)):
+            m = np.ascontiguousarray(m, dtype="<f4")
+            w.add_tensor(name + suffix, m.shape, GGMLType.F32, lambda m=m: m.view(np.uint8).reshape(-1))
+    return w.write()
+
+
 def load_weights(src: str | GGUFModelFiles, device, layer_range: range | None = None, tp_rank: int = 0, tp_size: int = 1,
-                 first_stage: bool = True, last_stage: bool = True, shard_vocab: bool = True) -> ModelWeights:
+                 first_stage: bool = True, last_stage: bool = True, shard_vocab: bool = True,
+                 lora: list[LoraAdapter] | None = None) -> ModelWeights:
     f = open_gguf(src) if isinstance(src, str) else src
+    lora = lora or []
     cfg = config_from_gguf(f.metadata, f.tensors)
     layer_range = range(cfg.n_layer) if layer_range is None else layer_range
     dev = torch.device(device)
@@ -104,12 +146,17 @@ def load_weights(src: str | GGUFModelFiles, device, layer_range: range | None = 
         if sub is not None:  # one expert of a stacked [n_expert, N, K] tensor
             raw = raw[sub]
             shape = shape[1:]
+        deltas = [d for d in (ad.delta(name) for ad in lora) if d is not None] if sub is None else []
         try:
+            if deltas:
+                raise ValueError("LoRA target: merge densely")
             raw2, shp = slice_raw(raw, t.ggml_type, shape, rows, cols)
         except ValueError:
             # K range not aligned to the quant block (tiny models / odd TP sizes): decode once, slice densely, keep fp16
             from ..gguf.quants import dequantize, quantize
             dense = dequantize(raw, t.ggml_type, shape)
+            for d in deltas:
+                dense = dense + d.reshape(dense.shape)
             if rows is not None:
                 dense = dense[rows[0]:rows[1]]
             if cols is not None:

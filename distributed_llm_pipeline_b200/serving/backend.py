@@ -20,6 +20,7 @@ import sys
 import threading
 
 from .orchestrator import build_service
+from ..utils.args import lora_from_args
 from .sampler import SamplingParams
 from .scheduler import Request
 
@@ -109,7 +110,7 @@ def main(argv=None):
     ap.add_argument("-b", "--batch-size", type=int, default=2048)
     ap.add_argument("--device", default="cuda")
     a = ap.parse_args(argv)
-    sched, info, logs = build_service(a.model, a.device, a.ctx_size, a.parallel, a.batch_size)
+    sched, info, logs = build_service(a.model, a.device, a.ctx_size, a.parallel, a.batch_size, lora=lora_from_args(a))
     for l in logs:
         sys.stderr.write(l)
     sys.stderr.flush()

@@ -20,6 +20,7 @@ import os
 import time
 import uuid
 
+from ..utils.args import lora_from_args
 from .sampler import SamplingParams
 from .scheduler import Request, Scheduler
 
@@ -345,7 +346,8 @@ class Orchestrator:
             await self._server.serve_forever()
 
 
-def build_service(model: str, device: str = "cuda", n_ctx: int = 2048, n_slots: int = 4, n_batch: int = 2048, page_size: int = 64):
+def build_service(model: str, device: str = "cuda", n_ctx: int = 2048, n_slots: int = 4, n_batch: int = 2048, page_size: int = 64,
+                  lora=None):
     """Load a GGUF checkpoint and return (scheduler, model_info, startup_logs)."""
     import torch
 
@@ -356,7 +358,7 @@ def build_service(model: str, device: str = "cuda", n_ctx: int = 2048, n_slots: 
     dev = device if (device != "cuda" or torch.cuda.is_available()) else "cpu"
     f = open_gguf(model)
     t0 = time.time()
-    w = load_weights(f, dev)
+    w = load_weights(f, dev, lora=lora)
     eng = LlamaEngine(w, n_ctx=n_ctx, max_seqs=n_slots + 1, page_size=page_size if dev != "cpu" else 16, max_batch_tokens=n_batch)
     tok = Tokenizer(f.metadata)
     cfg = w.cfg
@@ -383,7 +385,7 @@ def main(argv=None):
     ap.add_argument("--device", default="cuda")
     ap.add_argument("--static", default=STATIC_DIR)
     a = ap.parse_args(argv)
-    sched, info, logs = build_service(a.model, a.device, a.ctx_size, a.parallel, a.batch_size)
+    sched, info, logs = build_service(a.model, a.device, a.ctx_size, a.parallel, a.batch_size, lora=lora_from_args(a))
     sched.start()
     orch = Orchestrator(sched, info, a.static, a.predict, logs)
     print(f"dlp_b200 orchestrator ready: http://localhost:{a.port}", flush=True)

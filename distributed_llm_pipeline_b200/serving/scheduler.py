@@ -39,6 +39,7 @@ class Request:
     on_event: Callable[[str, str], None] | None = None  # ("token" | "log" | "done" | "error", content)
     ignore_eos: bool = False
     cache_prompt: bool = True
+    n_keep: int = 0             # tokens of the prompt that survive a context shift (-1 = the whole prompt)
     id: int = 0
     # filled in by the scheduler
     prompt_ids: list[int] = field(default_factory=list)
@@ -143,6 +144,7 @@ class Scheduler:
         self._stop = False
         self._thread: threading.Thread | None = None
         self._jobs: list = []
+        self.context_shift = False          # --context-shift: slide the window instead of stopping at n_ctx
         self.log = log or (lambda s: None)
 
     # ---- submission -------------------------------------------------------------------------------
@@ -345,7 +347,17 @@ class Scheduler:
         elif len(req.output_ids) >= req.n_predict:
             self._finish(s, "length")
         elif s.n_past + 1 >= self.eng.n_ctx:
-            self._finish(s, "length")  # context full (the reference stops as well unless --context-shift)
+            if self.context_shift and hasattr(self.eng, "shift_seq"):
+                # keep the first n_keep tokens, drop half of the rest (server-context.cpp:1944-2003)
+                n_keep = min(req.n_keep if req.n_keep >= 0 else len(req.prompt_ids), self.eng.n_ctx - 4)
+                n_discard = (s.n_past - n_keep) // 2
+                self.eng.shift_seq(s.sid, n_keep, n_discard)
+                del s.cache_tokens[n_keep:n_keep + n_discard]
+                s.n_past -= n_discard
+                self.metrics.add(context_shifts_total=1)
+                self._emit(req, "log", f"slot {s.idx}: context shift, kept {n_keep}, discarded {n_discard} tokens\n")
+            else:
+                self._finish(s, "length")  # context full (the reference stops as well unless --context-shift)
 
     def _finish(self, s: Slot, reason: str):
         req = s.req

@@ -38,6 +38,7 @@ COMMON = [
     Opt(("--tp-impl",), "fused (in-kernel NVLink all-reduce) | nccl (baseline)", "fused", str, "DLP_TP_IMPL", choices=("fused", "nccl")),
     Opt(("--rpc",), "comma separated host:port list of dlp-worker CPU stages", None, str, "DLP_ARG_RPC"),
     Opt(("-fa", "--flash-attn"), "accepted for compatibility: attention is always flash", "on", str, "DLP_ARG_FLASH_ATTN"),
+    Opt(("--lora",), "comma separated LoRA adapter GGUFs, each optionally path:scale (merged at load)", None, str, "DLP_ARG_LORA"),
     Opt(("--device",), "cuda | cpu", "cuda", str, "DLP_ARG_DEVICE"),
     Opt(("-v", "--verbose"), "debug logging", False, None, "DLP_ARG_VERBOSE", action="store_true"),
     Opt(("--log-file",), "also write logs to this file", None, str, "DLP_ARG_LOG_FILE"),
@@ -76,6 +77,8 @@ GENERATION = [
     Opt(("-n", "--predict", "--n-predict"), "tokens to generate", 200, int, "DLP_ARG_N_PREDICT"),
     Opt(("--ignore-eos",), "keep generating after EOS", False, None, action="store_true"),
     Opt(("-st", "--single-turn"), "exit after one reply", False, None, action="store_true"),
+    Opt(("--context-shift",), "slide the context window instead of stopping at n_ctx", False, None, "DLP_ARG_CONTEXT_SHIFT", action="store_true"),
+    Opt(("--keep",), "prompt tokens kept across a context shift (-1 = all)", 0, int, "DLP_ARG_KEEP"),
 ]
 
 
@@ -109,3 +112,15 @@ def sampling_from_args(a):
                           dynatemp_range=a.dynatemp_range, dynatemp_exponent=a.dynatemp_exp, xtc_probability=a.xtc_probability,
                           xtc_threshold=a.xtc_threshold, mirostat=a.mirostat, mirostat_tau=a.mirostat_ent,
                           mirostat_eta=a.mirostat_lr, grammar=grammar or "", json_schema=schema)
+
+
+def lora_from_args(a):
+    """`--lora a.gguf,b.gguf:0.5` -> [LoraAdapter] (reference flags `--lora` / `--lora-scaled`)."""
+    from ..models.weights import LoraAdapter
+    out = []
+    for item in (getattr(a, "lora", None) or "").split(","):
+        if not item:
+            continue
+        path, _, sc = item.rpartition(":") if item.count(":") and item.rsplit(":", 1)[1].replace(".", "", 1).isdigit() else (item, "", "")
+        out.append(LoraAdapter(path or item, float(sc) if sc else 1.0))
+    return out

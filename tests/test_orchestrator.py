@@ -187,3 +187,15 @@ def test_grammar_constrained_completion(server):
     assert set(body_txt) <= set("kario.t")
     r = sched.generate("json:", n_predict=24, sampling=SamplingParams(temperature=0.0, json_schema={"type": "boolean"}))
     assert r.text.strip() in ("true", "false") and r.finish_reason == "stop"
+
+
+def test_context_shift_keeps_generating_past_n_ctx(tmp_models):
+    sched, _, _ = build_service(tmp_models[("tiny", "F16")], device="cpu", n_ctx=48, n_slots=1, n_batch=32)
+    logs = []
+    r = sched.generate("a b c d e", n_predict=70, sampling=SamplingParams(temperature=0.0), ignore_eos=True)
+    assert r.finish_reason == "length" and len(r.output_ids) < 48            # default: stop when the context is full
+    sched.context_shift = True
+    r = sched.generate("a b c d e", n_predict=70, sampling=SamplingParams(temperature=0.0), ignore_eos=True, cache_prompt=False,
+                       n_keep=-1, on_event=lambda k, c: logs.append(c) if k == "log" else None)
+    assert len(r.output_ids) == 70 and any("context shift" in x for x in logs)
+    assert sched.metrics.c["context_shifts_total"] >= 1

@@ -85,3 +85,61 @@ def test_unknown_architecture_is_rejected():
     from distributed_llm_pipeline_b200.models.config import config_from_gguf
     with pytest.raises(NotImplementedError):
         config_from_gguf({"general.architecture": "gpt2"})
+
+
+def test_lora_adapter_is_merged_at_load(tmp_models, tmp_path):
+    """LoRA GGUF adapter (llama-adapter.cpp format): engine with the adapter == oracle with W + scale*alpha/r * B@A."""
+    import numpy as np
+    from distributed_llm_pipeline_b200.models.weights import LoraAdapter, write_lora_gguf
+    path = tmp_models[("tiny", "Q8_0")]
+    ref = ReferenceModel.from_gguf(path)
+    rng = np.random.default_rng(0)
+    r, alpha, scale = 4, 8.0, 0.5
+    deltas = {}
+    for name in ("blk.0.attn_q.weight", "blk.1.ffn_down.weight", "blk.1.attn_output.weight"):
+        out_f, in_f = ref.w[name].shape
+        deltas[name] = (rng.standard_normal((r, in_f)).astype(np.float32) * 0.05, rng.standard_normal((out_f, r)).astype(np.float32) * 0.05)
+    apath = write_lora_gguf(str(tmp_path / "adapter.gguf"), deltas, alpha)
+    base_logits = ref.forward(list(range(5, 15)), ref.new_cache(32))[-1]
+    for name, (a, b) in deltas.items():
+        ref.w[name] = ref.w[name] + scale * alpha / r * torch.from_numpy(b @ a)
+    want = ref.forward(list(range(5, 15)), ref.new_cache(32))[-1]
+    assert nmse(want, base_logits) > 1e-3                       # the adapter really changes the output
+    eng = LlamaEngine(load_weights(path, "cpu", lora=[LoraAdapter(apath, scale)]), n_ctx=64, max_seqs=1, page_size=16, max_batch_tokens=32)
+    got = eng.prefill(eng.alloc_seq(), list(range(5, 15)))
+    assert nmse(want, got.float().flatten()) < 1e-5
+
+
+def _gather_kv(eng, sid, il):
+    seq = eng.seqs[sid]
+    pages = torch.tensor(seq.pages, dtype=torch.long)
+    k = eng.kv.k[il][pages].permute(0, 2, 1, 3).reshape(-1, eng.Hkv, eng.D)[: seq.length]
+    v = eng.kv.v[il][pages].permute(0, 2, 1, 3).reshape(-1, eng.Hkv, eng.D)[: seq.length]
+    return k.float().clone(), v.float().clone()
+
+
+@pytest.mark.parametrize("key", [("tiny", "F16"), ("tiny-qwen2", "F16")])
+def test_copy_seq_and_context_shift(tmp_models, key):
+    """seq_cp duplicates a sequence; the context shift drops a middle span and re-rotates the surviving keys."""
+    eng = LlamaEngine(load_weights(tmp_models[key], "cpu"), n_ctx=64, max_seqs=3, page_size=16, max_batch_tokens=32)
+    toks = list(range(7, 27))
+    a, b = eng.alloc_seq(), eng.alloc_seq()
+    eng.prefill(a, toks)
+    eng.copy_seq(a, b)
+    la = eng.decode([a], [5], sample=False)[0].clone()
+    lb = eng.decode([b], [5], sample=False)[0].clone()
+    assert torch.equal(la, lb) and eng.seq_len(b) == 21
+    eng.truncate_seq(a, 20)
+    k_old, v_old = _gather_kv(eng, a, 1)
+    eng.shift_seq(a, n_keep=4, n_discard=6)
+    assert eng.seq_len(a) == 14
+    k_new, v_new = _gather_kv(eng, a, 1)
+    assert torch.equal(v_new[:4], v_old[:4]) and torch.equal(v_new[4:], v_old[10:20]) and torch.equal(k_new[:4], k_old[:4])
+    # layer 0 keys depend only on (token, position): after the shift they equal a fresh prefill of the surviving tokens
+    k0, _ = _gather_kv(eng, a, 0)
+    c = eng.alloc_seq()
+    eng.prefill(c, toks[:4] + toks[10:])
+    k0_fresh, _ = _gather_kv(eng, c, 0)
+    assert nmse(k0_fresh, k0) < 1e-5
+    nxt = eng.decode([a], [9], sample=False)[0]             # and decoding continues from position 14
+    assert torch.isfinite(nxt).all() and eng.seq_len(a) == 15

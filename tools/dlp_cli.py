@@ -11,7 +11,7 @@ import time
 
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 
-from distributed_llm_pipeline_b200.utils.args import COMMON, GENERATION, SAMPLING, SPECULATIVE, build_parser, sampling_from_args  # noqa: E402
+from distributed_llm_pipeline_b200.utils.args import COMMON, GENERATION, SAMPLING, SPECULATIVE, build_parser, lora_from_args, sampling_from_args  # noqa: E402
 from distributed_llm_pipeline_b200.utils.log import get_logger  # noqa: E402
 
 
@@ -40,7 +40,7 @@ def main(argv=None):
         from distributed_llm_pipeline_b200.models.weights import load_weights
         dev = a.device if (a.device != "cuda" or torch.cuda.is_available()) else "cpu"
         f = open_gguf(a.model)
-        w = load_weights(f, dev)
+        w = load_weights(f, dev, lora=lora_from_args(a))
         eng = LlamaEngine(w, n_ctx=a.ctx_size, max_seqs=a.parallel, page_size=64 if dev != "cpu" else 16,
                           max_batch_tokens=min(a.batch_size, a.ubatch_size))
         tok = Tokenizer(f.metadata)
@@ -64,6 +64,7 @@ def main(argv=None):
         log.flush()
         return
     sched = Scheduler(eng, tok, n_batch=a.batch_size)
+    sched.context_shift = a.context_shift
 
     def on_event(kind, content):
         if kind == "token":
@@ -73,7 +74,7 @@ def main(argv=None):
             log.info(content.rstrip("\n"))
 
     while True:
-        req = sched.generate(prompt, n_predict=a.predict, sampling=sampling_from_args(a), ignore_eos=a.ignore_eos, on_event=on_event)
+        req = sched.generate(prompt, n_predict=a.predict, sampling=sampling_from_args(a), ignore_eos=a.ignore_eos, on_event=on_event, n_keep=a.keep)
         sys.stdout.write("\n")
         t = req.timings()
         log.info(f"prompt eval: {t['prompt_n']} tokens, {t['prompt_per_second']} tok/s | eval: {t['predicted_n']} tokens, {t['predicted_per_second']} tok/s")
