@@ -225,10 +225,11 @@ int dlp_rope_kv(const void* qkv, int qkv_is_f16, const int32_t* pos, const int32
 int dlp_rope_kv_ex(const void* qkv, int qkv_is_f16, const int32_t* pos, const int32_t* slot, const float* inv_freq,
                    void* q_out, void* k_cache, void* v_cache, int T, int Hq, int Hkv, int D, int n_rot, int page_size,
                    int neox, float q_scale, const float* bias, const float* q_norm, const float* k_norm, float eps,
-                   void* stream) {
+                   const void* pf0, size_t pf0_bytes, const void* pf1, size_t pf1_bytes, void* stream) {
     DLP_REQUIRE(qkv && pos && slot && inv_freq && q_out && k_cache && v_cache, "dlp_rope_kv_ex: null argument");
     return rope_kv(qkv, qkv_is_f16, pos, slot, inv_freq, (__half*)q_out, (__half*)k_cache, (__half*)v_cache, T, Hq, Hkv,
-                   D, n_rot, page_size, neox, q_scale, (cudaStream_t)stream, bias, q_norm, k_norm, eps);
+                   D, n_rot, page_size, neox, q_scale, (cudaStream_t)stream, bias, q_norm, k_norm, eps, pf0, pf0_bytes, pf1,
+                   pf1_bytes);
 }
 
 int dlp_swiglu(const void* gate_up, int is_f16, void* out_f16, int T, int F, int ld_in, void* stream) {

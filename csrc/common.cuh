@@ -229,6 +229,20 @@ __device__ __forceinline__ bool elect_one() {
 __device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
 __device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
 __device__ __forceinline__ void prefetch_l2(const void* p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p)); }
+// One instruction pulls up to `bytes` (multiple of 16, 16 B aligned) of global memory into L2: lets a small kernel warm
+// the weights of the mat-vec that follows it while HBM would otherwise idle.
+__device__ __forceinline__ void bulk_prefetch_l2(const void* p, unsigned bytes) {
+    asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(p), "r"(bytes) : "memory");
+}
+// This CTA's share (CTA `b` of `nb`) of a [ptr, ptr + bytes) range, in 32 KB pieces.  Call from one thread.
+__device__ __forceinline__ void prefetch_share_l2(const char* ptr, unsigned bytes, unsigned b, unsigned nb) {
+    if (ptr == nullptr || bytes == 0) return;
+    const unsigned per = ((bytes + nb - 1) / nb + 4095u) & ~4095u;
+    const unsigned start = b * per;
+    if (start >= bytes) return;                       // the `start + per` below cannot wrap: start < bytes <= 4 GiB - per
+    const unsigned end = bytes - start < per ? bytes : start + per;
+    for (unsigned o = start; o < end; o += 32768u) bulk_prefetch_l2(ptr + o, (end - o < 32768u ? end - o : 32768u) & ~15u);
+}
 
 #endif  // __CUDACC__
 

@@ -140,13 +140,18 @@ __global__ void rope_kv_kernel(const InT* __restrict__ qkv, const int* __restric
                                const float* __restrict__ inv_freq, __half* __restrict__ q_out, __half* __restrict__ kc,
                                __half* __restrict__ vc, int Hq, int Hkv, int D, int n_rot, int page_size, int neox, float q_scale,
                                const float* __restrict__ bias, const float* __restrict__ qn, const float* __restrict__ kn,
-                               float eps) {
+                               float eps, const char* __restrict__ pf0, unsigned pf0_bytes, const char* __restrict__ pf1,
+                               unsigned pf1_bytes) {
     // one (head, pair) per thread: grid = (T, ceil(H * D/2 / 256)) so that even a single decode token spreads over
     // a dozen CTAs and every load is issued at once (a serial per-thread loop here is pure latency)
     const int t = blockIdx.x;
     const int H = Hq + 2 * Hkv;
     const int half_d = D / 2;
     const int idx = blockIdx.y * blockDim.x + threadIdx.x;
+    if (threadIdx.x == 0) {   // weights of the next mat-vec (Wo) -> L2 while this kernel and attention run; no dependency
+        prefetch_share_l2(pf0, pf0_bytes, blockIdx.x * gridDim.y + blockIdx.y, gridDim.x * gridDim.y);
+        prefetch_share_l2(pf1, pf1_bytes, blockIdx.x * gridDim.y + blockIdx.y, gridDim.x * gridDim.y);
+    }
     pdl_wait();
     pdl_launch_dependents();
     const bool live = idx < H * half_d;
@@ -209,13 +214,16 @@ __global__ void rope_kv_kernel(const InT* __restrict__ qkv, const int* __restric
 
 int rope_kv(const void* qkv, int qkv_is_f16, const int* pos, const int* slot, const float* inv_freq, __half* q_out,
             __half* kc, __half* vc, int T, int Hq, int Hkv, int D, int n_rot, int page_size, int neox, float q_scale,
-            cudaStream_t s, const float* bias, const float* qn, const float* kn, float eps) {
+            cudaStream_t s, const float* bias, const float* qn, const float* kn, float eps, const void* pf0, size_t pf0_bytes,
+            const void* pf1, size_t pf1_bytes) {
+    DLP_REQUIRE(pf0_bytes < (1ull << 32) && pf1_bytes < (1ull << 32) && pf0_bytes % 16 == 0 && pf1_bytes % 16 == 0 &&
+                ((uintptr_t)pf0 & 15) == 0 && ((uintptr_t)pf1 & 15) == 0, "rope_kv: bad prefetch range");
     DLP_REQUIRE(T > 0 && D % 2 == 0 && n_rot <= D && n_rot % 2 == 0, "rope_kv: bad shape");
     DLP_REQUIRE((qn == nullptr) == (kn == nullptr), "rope_kv: q/k norm weights come as a pair");
     const bool ex = bias != nullptr || qn != nullptr;
     if (qn != nullptr) DLP_REQUIRE(256 % (D / 2) == 0 && (D / 2 >= 32 || (D / 2 & (D / 2 - 1)) == 0), "rope_kv: qk-norm needs D/2 | 256 (D=%d)", D);
     const dim3 grid(T, ((Hq + 2 * Hkv) * (D / 2) + 255) / 256);
-#define DLP_ROPE_LAUNCH(TY, EXF) DLP_CHECK_CUDA(launch_pdl(rope_kv_kernel<TY, EXF>, grid, dim3(256), 0, s, (const TY*)qkv, pos, slot, inv_freq, q_out, kc, vc, Hq, Hkv, D, n_rot, page_size, neox, q_scale, bias, qn, kn, eps))
+#define DLP_ROPE_LAUNCH(TY, EXF) DLP_CHECK_CUDA(launch_pdl(rope_kv_kernel<TY, EXF>, grid, dim3(256), 0, s, (const TY*)qkv, pos, slot, inv_freq, q_out, kc, vc, Hq, Hkv, D, n_rot, page_size, neox, q_scale, bias, qn, kn, eps, (const char*)pf0, (unsigned)pf0_bytes, (const char*)pf1, (unsigned)pf1_bytes))
     if (qkv_is_f16) { if (ex) DLP_ROPE_LAUNCH(__half, true); else DLP_ROPE_LAUNCH(__half, false); }
     else            { if (ex) DLP_ROPE_LAUNCH(float, true);  else DLP_ROPE_LAUNCH(float, false); }
 #undef DLP_ROPE_LAUNCH

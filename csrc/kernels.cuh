@@ -100,7 +100,8 @@ int dequant_rows_f16(const QWeight& w, int wtype, const int* row_ids, int n_rows
 int rmsnorm(float* h, const float* delta, const float* w, __half* out, int T, int E, float eps, cudaStream_t s);
 int rope_kv(const void* qkv, int qkv_is_f16, const int* pos, const int* slot, const float* inv_freq, __half* q_out,
             __half* kc, __half* vc, int T, int Hq, int Hkv, int D, int n_rot, int page_size, int neox, float q_scale,
-            cudaStream_t s, const float* bias = nullptr, const float* qn = nullptr, const float* kn = nullptr, float eps = 0.f);
+            cudaStream_t s, const float* bias = nullptr, const float* qn = nullptr, const float* kn = nullptr, float eps = 0.f,
+            const void* pf0 = nullptr, size_t pf0_bytes = 0, const void* pf1 = nullptr, size_t pf1_bytes = 0);
 int swiglu(const void* gu, int is_f16, __half* out, int T, int F, int ld_in, cudaStream_t s);
 int advance(int* seq_len, const int* active, int* pos, int* slot, int* kv_len, const int* block_table, int max_pages,
             int page_size, int n, cudaStream_t s);

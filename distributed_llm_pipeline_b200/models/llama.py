@@ -236,7 +236,7 @@ class LlamaEngine:
         lw = self.w.layers[il]
         return ops.rope_kv(qkv, self.pos[:T], self.slot[:T], self.inv_freq, self.kv.k[il], self.kv.v[il], self.Hq, self.Hkv,
                            self.D, self.cfg.rope_neox, q_out=self.q[:T], bias=lw.qkv_bias, q_norm=lw.q_norm, k_norm=lw.k_norm,
-                           eps=self.cfg.rms_eps)
+                           eps=self.cfg.rms_eps, prefetch=lw.wo if T <= 4 else None)
 
     # ---- one transformer layer over T tokens held in the static buffers ------------------------
     def _layer(self, il: int, T: int, attn_fn):

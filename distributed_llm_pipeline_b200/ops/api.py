@@ -18,6 +18,9 @@ _OUT = {"f16": OUT_F16, "f32": OUT_F32, "add": OUT_ADD_F32, "swiglu": OUT_SWIGLU
 
 import os as _os
 TWO_PASS_DEQUANT = _os.environ.get("DLP_GEMM_DEQUANT_SCRATCH", "0") == "1"
+# RoPE kernel warms L2 with the O-projection weights (decode).  Measured slower on B200 (F16 312.8 vs 346.1 tok/s, Q8_0 371 vs
+# 390, profiles/r1_l2_prefetch_ab.txt): kept as an experiment switch, off by default.
+PREFETCH_NEXT = _os.environ.get("DLP_L2_PREFETCH", "0") == "1"
 
 # launch counter: every native kernel launch issued through this module (bench.py reports it)
 launch_count = 0
@@ -150,9 +153,10 @@ def gemm_f16(w: torch.Tensor, x: torch.Tensor, out: torch.Tensor, epilogue: int 
 def rope_kv(qkv: torch.Tensor, pos: torch.Tensor, slot: torch.Tensor, inv_freq: torch.Tensor, k_cache: torch.Tensor,
             v_cache: torch.Tensor, n_head: int, n_head_kv: int, head_dim: int, neox: bool = False,
             q_out: torch.Tensor | None = None, bias: torch.Tensor | None = None, q_norm: torch.Tensor | None = None,
-            k_norm: torch.Tensor | None = None, eps: float = 1e-6) -> torch.Tensor:
+            k_norm: torch.Tensor | None = None, eps: float = 1e-6, prefetch=None) -> torch.Tensor:
     """Rotate Q,K; write K,V into the paged cache [pages, Hkv, page, D]; return q (fp16 [T, Hq*D], pre-scaled).
-    Optional `bias` (qwen2) is added to q|k|v first; `q_norm`/`k_norm` (qwen3) are per-head RMSNorm weights."""
+    Optional `bias` (qwen2) is added to q|k|v first; `q_norm`/`k_norm` (qwen3) are per-head RMSNorm weights.
+    `prefetch`: a DeviceWeight whose planes (the next mat-vec's weights) the kernel pulls into L2 while it runs."""
     T = qkv.shape[0]
     page_size = k_cache.shape[2]
     n_rot = inv_freq.numel() * 2
@@ -179,12 +183,18 @@ def rope_kv(qkv: torch.Tensor, pos: torch.Tensor, slot: torch.Tensor, inv_freq: 
         k_cache[pg, :, off] = k[ok].to(k_cache.dtype)
         v_cache[pg, :, off] = v[ok].to(v_cache.dtype)
         return q_out
-    if bias is not None or q_norm is not None:
+    pf = []
+    if prefetch is not None and PREFETCH_NEXT and prefetch.dense is None:
+        pf = [(pl.data_ptr(), pl.numel() * pl.element_size()) for pl in prefetch.planes[:2]]
+        pf = [(p, n) for p, n in pf if p % 16 == 0 and n % 16 == 0 and n < 2**32]
+    if bias is not None or q_norm is not None or pf:
+        pf += [(None, 0)] * (2 - len(pf))
         _lib.check(_lib.load().dlp_rope_kv_ex(
             qkv.data_ptr(), int(qkv.dtype == torch.float16), pos.data_ptr(), slot.data_ptr(), inv_freq.data_ptr(),
             q_out.data_ptr(), k_cache.data_ptr(), v_cache.data_ptr(), T, n_head, n_head_kv, head_dim, n_rot, page_size,
             int(neox), q_scale, bias.data_ptr() if bias is not None else None, q_norm.data_ptr() if q_norm is not None else None,
-            k_norm.data_ptr() if k_norm is not None else None, float(eps), _stream()), "rope_kv_ex")
+            k_norm.data_ptr() if k_norm is not None else None, float(eps), pf[0][0], pf[0][1], pf[1][0], pf[1][1], _stream()),
+            "rope_kv_ex")
         _count()
         return q_out
     _lib.check(_lib.load().dlp_rope_kv(qkv.data_ptr(), int(qkv.dtype == torch.float16), pos.data_ptr(), slot.data_ptr(),

@@ -51,7 +51,8 @@ def _declare(lib):
         "dlp_dequant_rows_f16": (i32, [W, vp, i32, vp, i32, vp]),
         "dlp_rmsnorm": (i32, [vp, vp, vp, vp, i32, i32, f32, vp]),
         "dlp_rope_kv": (i32, [vp, i32, vp, vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, i32, i32, f32, vp]),
-        "dlp_rope_kv_ex": (i32, [vp, i32, vp, vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, i32, i32, f32, vp, vp, vp, f32, vp]),
+        "dlp_rope_kv_ex": (i32, [vp, i32, vp, vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, i32, i32, f32, vp, vp, vp, f32,
+                                 vp, C.c_size_t, vp, C.c_size_t, vp]),
         "dlp_swiglu": (i32, [vp, i32, vp, i32, i32, i32, vp]),
         "dlp_advance": (i32, [vp, vp, vp, vp, vp, vp, i32, i32, i32, vp]),
         "dlp_attn_paged": (i32, [vp, vp, vp, vp, vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, i32, i32, vp]),

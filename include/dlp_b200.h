@@ -80,11 +80,14 @@ int dlp_rope_kv(const void* qkv, int qkv_is_f16, const int32_t* pos, const int32
                 int neox, float q_scale, void* stream);
 /* Same, for the other architecture families: `bias` [(Hq+2Hkv)*D] fp32 is added to q|k|v first (qwen2,
  * llama.cpp/src/models/qwen2.cpp), `q_norm`/`k_norm` [D] fp32 are per-head RMSNorm weights applied before the rotation
- * (qwen3, llama.cpp/src/models/qwen3.cpp).  Any of them may be NULL (q_norm/k_norm only as a pair). */
+ * (qwen3, llama.cpp/src/models/qwen3.cpp).  Any of them may be NULL (q_norm/k_norm only as a pair).
+ * `pf0`/`pf1` (+ byte counts, 16 B aligned, < 4 GiB; NULL/0 = none) name up to two memory ranges - the planes of the weight
+ * the next mat-vec will stream - that the kernel asks L2 to fetch (cp.async.bulk.prefetch.L2) before it waits on its
+ * own inputs, so HBM keeps working through this kernel and the attention kernel that follows. */
 int dlp_rope_kv_ex(const void* qkv, int qkv_is_f16, const int32_t* pos, const int32_t* slot, const float* inv_freq,
                    void* q_out, void* k_cache, void* v_cache, int T, int Hq, int Hkv, int D, int n_rot, int page_size,
                    int neox, float q_scale, const float* bias, const float* q_norm, const float* k_norm, float eps,
-                   void* stream);
+                   const void* pf0, size_t pf0_bytes, const void* pf1, size_t pf1_bytes, void* stream);
 
 int dlp_swiglu(const void* gate_up, int is_f16, void* out_f16, int T, int F, int ld_in, void* stream);
 
