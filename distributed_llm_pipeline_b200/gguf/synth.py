@@ -169,6 +169,13 @@ def write_synthetic_gguf(path: str, cfg: ModelConfig, ftype: str = "F16", seed: 
     if cfg.head_dim * cfg.n_head != cfg.n_embd:
         w.add(f"{a}.attention.key_length", cfg.head_dim, ValueType.UINT32)
         w.add(f"{a}.attention.value_length", cfg.head_dim, ValueType.UINT32)
+    if cfg.yarn_factor > 1.0:
+        w.add(f"{a}.rope.scaling.type", "yarn")
+        w.add(f"{a}.rope.scaling.factor", float(cfg.yarn_factor), ValueType.FLOAT32)
+        w.add(f"{a}.rope.scaling.original_context_length", int(cfg.yarn_orig_ctx), ValueType.UINT32)
+    elif cfg.rope_scale_linear != 1.0:
+        w.add(f"{a}.rope.scaling.type", "linear")
+        w.add(f"{a}.rope.scaling.factor", float(1.0 / cfg.rope_scale_linear), ValueType.FLOAT32)
     if cfg.is_moe:
         w.add(f"{a}.expert_count", cfg.n_expert, ValueType.UINT32)
         w.add(f"{a}.expert_used_count", cfg.n_expert_used, ValueType.UINT32)

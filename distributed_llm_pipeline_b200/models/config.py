@@ -27,6 +27,13 @@ class ModelConfig:
     rope_dim: int = 128
     rope_neox: bool = False  # llama arch = adjacent-pair ("norm") rotation
     rope_scale_linear: float = 1.0
+    # YaRN context extension (`llama.cpp/src/llama-context.cpp:82-132`, kernel `ggml-cuda/rope.cu:15-40`): factor > 1 enables it
+    yarn_factor: float = 1.0
+    yarn_orig_ctx: int = 0
+    yarn_ext_factor: float = 1.0
+    yarn_attn_factor: float = 1.0
+    yarn_beta_fast: float = 32.0
+    yarn_beta_slow: float = 1.0
     n_expert: int = 0
     n_expert_used: int = 0
     bos_id: int = 1
@@ -144,6 +151,12 @@ def config_from_gguf(meta: dict[str, Any], tensors: dict | None = None) -> Model
     scale = 1.0
     if meta.get(f"{arch}.rope.scaling.type", "none") == "linear":
         scale = 1.0 / float(meta.get(f"{arch}.rope.scaling.factor", 1.0))
+    yarn = {}
+    if meta.get(f"{arch}.rope.scaling.type", "none") == "yarn":
+        yarn = dict(yarn_factor=float(g("rope.scaling.factor", 1.0)),
+                    yarn_orig_ctx=int(g("rope.scaling.original_context_length", g("context_length", 2048))),
+                    yarn_ext_factor=float(g("rope.scaling.yarn_ext_factor", 1.0)), yarn_attn_factor=float(g("rope.scaling.attn_factor", 1.0)),
+                    yarn_beta_fast=float(g("rope.scaling.yarn_beta_fast", 32.0)), yarn_beta_slow=float(g("rope.scaling.yarn_beta_slow", 1.0)))
     tie = tensors is not None and "output.weight" not in tensors
     return ModelConfig(
         name=str(meta.get("general.name", arch)), arch=arch, vocab_size=int(vocab), n_embd=n_embd,
@@ -156,4 +169,4 @@ def config_from_gguf(meta: dict[str, Any], tensors: dict | None = None) -> Model
         fused_qkv=arch == "phi3" or (tensors is not None and "blk.0.attn_qkv.weight" in tensors),
         n_expert=int(g("expert_count", 0) or 0), n_expert_used=int(g("expert_used_count", 0) or 0),
         bos_id=int(meta.get("tokenizer.ggml.bos_token_id", 1)), eos_id=int(meta.get("tokenizer.ggml.eos_token_id", 2)),
-        tie_embeddings=tie)
+        tie_embeddings=tie, **yarn)

@@ -19,7 +19,7 @@ import torch
 
 from ..ops import api as ops
 from .config import ModelConfig
-from .reference import rope_inv_freq
+from .reference import rope_attn_scale, rope_inv_freq
 from .weights import ModelWeights
 
 
@@ -104,6 +104,7 @@ class LlamaEngine:
             n_pages = max_pages * max_seqs
         self.kv = PagedKVCache(cfg, weights.layer_range, self.Hkv, n_pages, page_size, max_seqs, max_pages, dev)
         self.inv_freq = rope_inv_freq(cfg, weights.rope_freqs.cpu() if weights.rope_freqs is not None else None).to(dev)
+        self.attn_scale = rope_attn_scale(cfg)
         self.seqs: dict[int, Sequence] = {}
         self._free_sids = list(range(max_seqs - 1, -1, -1))
         M = self.max_tokens + 8   # head-room: the sequence-parallel path pads T up to a multiple of tp
@@ -147,6 +148,7 @@ class LlamaEngine:
         self.scratch = None  # fp16 decode buffer for block-quantised weights on the GEMM path (allocated lazily)
         self._graphs: dict[tuple, torch.cuda.CUDAGraph] = {}
         self.sampling = dict(top_k=40, top_p=0.95, min_p=0.05, temp=0.0, seed=0)
+        self.eval_callback = None      # fn(name, layer, tensor) called after every layer (eager paths only; disables graphs)
 
     # ---- sequence management ------------------------------------------------------------------
     def alloc_seq(self) -> int:
@@ -236,7 +238,7 @@ class LlamaEngine:
         lw = self.w.layers[il]
         return ops.rope_kv(qkv, self.pos[:T], self.slot[:T], self.inv_freq, self.kv.k[il], self.kv.v[il], self.Hq, self.Hkv,
                            self.D, self.cfg.rope_neox, q_out=self.q[:T], bias=lw.qkv_bias, q_norm=lw.q_norm, k_norm=lw.k_norm,
-                           eps=self.cfg.rms_eps, prefetch=lw.wo if T <= 4 else None)
+                           eps=self.cfg.rms_eps, prefetch=lw.wo if T <= 4 else None, attn_scale=self.attn_scale)
 
     # ---- one transformer layer over T tokens held in the static buffers ------------------------
     def _layer(self, il: int, T: int, attn_fn):
@@ -377,6 +379,16 @@ class LlamaEngine:
             return
         for il in self.w.layer_range:
             self._layer(il, T, attn_fn)
+            if self.eval_callback is not None:      # tensor inspection hook (ggml-backend.cpp:1584-1616, examples/eval-callback)
+                self.eval_callback("l_out", il, self.h[:T])
+
+    def memory_breakdown(self) -> dict:
+        """Bytes held on this rank's device by category (`llama_memory_breakdown_print`, llama.h:1501)."""
+        def nb(*ts):
+            return sum(t.numel() * t.element_size() for t in ts if t is not None)
+        act = nb(self.h, self.delta, self.xn, self.qkv32, self.qkv16, self.q, self.att, self.act, self.logits, *(self.attn_ws or ()))
+        return {"model": self.w.nbytes(), "kv_cache": self.kv.bytes(), "compute": act,
+                "graphs": len(self._graphs), "device": str(self.device)}
 
     def _forward_sp(self, T: int, attn_fn, logits_row: int | None):
         """Tensor-parallel forward for T > 4 tokens in the sequence-parallel layout (parallel/fused.py): the residual
@@ -582,7 +594,7 @@ class LlamaEngine:
             self.h[:B].copy_(hidden_in)
         moe_host = self.cfg.is_moe and not (B <= 4 and self.comm.tp_size == 1 and self.cfg.n_expert <= 32 and
                                             next(iter(self.w.layers.values())).e_gate_s is not None)
-        graphable = (use_graph and self.device.type == "cuda" and not moe_host
+        graphable = (use_graph and self.eval_callback is None and self.device.type == "cuda" and not moe_host
                      and not getattr(self.comm, "no_graph", False)
                      and not (self.fused_tp and B > 4))   # SP path passes host-side epochs as kernel arguments
         if graphable:

@@ -29,10 +29,29 @@ def nmse(a: torch.Tensor, b: torch.Tensor) -> float:
 
 def rope_inv_freq(cfg: ModelConfig, freq_factors: torch.Tensor | None = None) -> torch.Tensor:
     i = torch.arange(0, cfg.rope_dim // 2, dtype=torch.float64)
-    inv = cfg.rope_theta ** (-2.0 * i / cfg.rope_dim) * cfg.rope_scale_linear
+    inv = cfg.rope_theta ** (-2.0 * i / cfg.rope_dim)
     if freq_factors is not None:
         inv = inv / freq_factors.double()
+    if cfg.yarn_factor > 1.0:
+        # YaRN: interpolate low frequencies by 1/factor, keep high frequencies, blend over the correction range
+        # (`rope_yarn` / `ggml_rope_yarn_corr_dims`, ggml-cuda/rope.cu:15-40, ggml.c)
+        def corr_dim(n_rot):
+            return cfg.rope_dim * math.log(cfg.yarn_orig_ctx / (n_rot * 2 * math.pi)) / (2 * math.log(cfg.rope_theta))
+        low = max(0.0, math.floor(corr_dim(cfg.yarn_beta_fast)))
+        high = min(cfg.rope_dim - 1.0, math.ceil(corr_dim(cfg.yarn_beta_slow)))
+        ramp = (1.0 - ((i - low) / max(0.001, high - low)).clamp(0, 1)) * cfg.yarn_ext_factor
+        inv = inv / cfg.yarn_factor * (1 - ramp) + inv * ramp
+    else:
+        inv = inv * cfg.rope_scale_linear
     return inv.float()
+
+
+def rope_attn_scale(cfg: ModelConfig) -> float:
+    """Multiplier on the attention logits from YaRN's magnitude correction (cos/sin are scaled by
+    mscale = attn_factor * (1 + 0.1 ln(factor)) on both Q and K, i.e. the scores by mscale^2)."""
+    if cfg.yarn_factor <= 1.0 or cfg.yarn_ext_factor == 0.0:
+        return 1.0
+    return (cfg.yarn_attn_factor * (1.0 + 0.1 * math.log(cfg.yarn_factor))) ** 2
 
 
 def apply_rope(x: torch.Tensor, pos: torch.Tensor, inv_freq: torch.Tensor, neox: bool) -> torch.Tensor:
@@ -109,7 +128,7 @@ class ReferenceModel:
         V = cache.v[il][: start + T]
         Kx = K.repeat_interleave(c.n_gqa, dim=1)
         Vx = V.repeat_interleave(c.n_gqa, dim=1)
-        scores = torch.einsum("thd,shd->hts", q, Kx) / math.sqrt(c.head_dim)
+        scores = torch.einsum("thd,shd->hts", q, Kx) * (rope_attn_scale(c) / math.sqrt(c.head_dim))
         kpos = torch.arange(start + T)
         mask = kpos[None, :] > pos[:, None]
         scores = scores.masked_fill(mask[None], float("-inf"))

@@ -153,14 +153,14 @@ def gemm_f16(w: torch.Tensor, x: torch.Tensor, out: torch.Tensor, epilogue: int 
 def rope_kv(qkv: torch.Tensor, pos: torch.Tensor, slot: torch.Tensor, inv_freq: torch.Tensor, k_cache: torch.Tensor,
             v_cache: torch.Tensor, n_head: int, n_head_kv: int, head_dim: int, neox: bool = False,
             q_out: torch.Tensor | None = None, bias: torch.Tensor | None = None, q_norm: torch.Tensor | None = None,
-            k_norm: torch.Tensor | None = None, eps: float = 1e-6, prefetch=None) -> torch.Tensor:
+            k_norm: torch.Tensor | None = None, eps: float = 1e-6, prefetch=None, attn_scale: float = 1.0) -> torch.Tensor:
     """Rotate Q,K; write K,V into the paged cache [pages, Hkv, page, D]; return q (fp16 [T, Hq*D], pre-scaled).
     Optional `bias` (qwen2) is added to q|k|v first; `q_norm`/`k_norm` (qwen3) are per-head RMSNorm weights.
     `prefetch`: a DeviceWeight whose planes (the next mat-vec's weights) the kernel pulls into L2 while it runs."""
     T = qkv.shape[0]
     page_size = k_cache.shape[2]
     n_rot = inv_freq.numel() * 2
-    q_scale = 1.0 / math.sqrt(head_dim)
+    q_scale = attn_scale / math.sqrt(head_dim)     # attn_scale: YaRN magnitude correction folded into the pre-scaled Q
     if q_out is None:
         q_out = torch.empty(T, n_head * head_dim, dtype=torch.float16, device=qkv.device)
     if not native(qkv):

@@ -54,7 +54,7 @@ class DeviceWeight:
 
     @property
     def nbytes(self) -> int:
-        return sum(p.numel() * p.element_size() for p in self.planes)
+        return sum(p.numel() * p.element_size() for p in self.planes) + (self.dense.numel() * self.dense.element_size() if self.dense is not None else 0)
 
     @property
     def c(self) -> dlp_weight:

@@ -46,17 +46,34 @@ def apply_chat_template(meta: dict, messages: list[dict]) -> str:
     if "<|im_start|>" in tmpl:
         out = "".join(f"<|im_start|>{m['role']}\n{m['content']}<|im_end|>\n" for m in messages)
         return out + "<|im_start|>assistant\n"
+    if "<start_of_turn>" in tmpl:      # gemma
+        out = "".join(f"<start_of_turn>{'model' if m['role'] == 'assistant' else 'user'}\n{m['content']}<end_of_turn>\n" for m in messages)
+        return out + "<start_of_turn>model\n"
+    if "<|assistant|>" in tmpl and "<|end|>" in tmpl:   # phi-3
+        return "".join(f"<|{m['role']}|>\n{m['content']}<|end|>\n" for m in messages) + "<|assistant|>\n"
+    if "<|assistant|>" in tmpl:        # zephyr
+        return "".join(f"<|{m['role']}|>\n{m['content']}</s>\n" for m in messages) + "<|assistant|>\n"
     if "[INST]" in tmpl:
-        out = ""
+        out, sys_txt = "", ""
         for m in messages:
-            out += f"[INST] {m['content']} [/INST]" if m["role"] == "user" else f" {m['content']}</s>"
+            if m["role"] == "system":      # llama-2 style: the system text rides inside the first [INST] block
+                sys_txt = f"<<SYS>>\n{m['content']}\n<</SYS>>\n\n" if "<<SYS>>" in tmpl else m["content"] + "\n\n"
+            elif m["role"] == "user":
+                out += f"[INST] {sys_txt}{m['content']} [/INST]"
+                sys_txt = ""
+            else:
+                out += f" {m['content']}</s>"
         return out
     return "\n".join(m["content"] for m in messages)
 
 
 class Orchestrator:
     def __init__(self, scheduler: Scheduler, model_info: dict | None = None, static_dir: str = STATIC_DIR, n_predict: int = 200,
-                 startup_logs: list[str] | None = None):
+                 startup_logs: list[str] | None = None, api_key: str | None = None, max_queue: int = 0,
+                 slot_save_path: str | None = None):
+        self.api_key = api_key            # --api-key: Bearer token required on every API route except /health (server-http.cpp)
+        self.max_queue = max_queue        # > 0: refuse new work with 503 once this many requests wait (request queueing, PDF p.6)
+        self.slot_save_path = slot_save_path
         self.sched = scheduler
         self.info = model_info or {}
         self.static_dir = static_dir
@@ -107,7 +124,8 @@ class Orchestrator:
                 if req is None:
                     break
                 method, target, headers, body = req
-                path = target.split("?", 1)[0]
+                path, _, query = target.partition("?")
+                self._query = dict(kv.partition("=")[::2] for kv in query.split("&") if kv)
                 keep = await self.route(method, path, headers, body, reader, writer)
                 if not keep or headers.get("connection", "").lower() == "close":
                     break
@@ -125,10 +143,35 @@ class Orchestrator:
                                                        ("content-length", "0")]))
             await writer.drain()
             return True
+        is_api = method == "POST" or path in ("/metrics", "/slots", "/props", "/v1/models") or path.startswith("/slots/")
+        if self.api_key and is_api and path != "/health":
+            auth = headers.get("authorization", "")
+            if auth != f"Bearer {self.api_key}" and headers.get("x-api-key", "") != self.api_key:
+                await self._json(writer, {"error": {"code": 401, "message": "Invalid API Key", "type": "authentication_error"}}, "401 Unauthorized")
+                return True
+        if self.max_queue > 0 and method == "POST" and len(self.sched.queue) >= self.max_queue and path not in ("/tokenize", "/detokenize"):
+            await self._json(writer, {"error": {"code": 503, "message": "request queue is full", "type": "unavailable_error"}}, "503 Service Unavailable")
+            return True
         try:
             if method == "POST" and path == "/chat":
                 await self.chat(body, writer)
                 return False
+            if method == "POST" and path.startswith("/slots/"):
+                return await self.slot_action(path, json.loads(body or b"{}"), writer)
+            if method == "POST" and path == "/apply-template":
+                await self._json(writer, {"prompt": apply_chat_template(self.info.get("metadata", {}), json.loads(body or b"{}").get("messages", []))})
+                return True
+            if method == "POST" and path == "/infill":
+                d = json.loads(body or b"{}")
+                fim = self.sched.tok.fim_ids()
+                if fim is None:
+                    await self._json(writer, {"error": "the model's vocabulary has no fill-in-the-middle tokens"}, "501 Not Implemented")
+                    return True
+                t = self.sched.tok
+                ids = [fim["pre"]] + t.encode(d.get("input_prefix", ""), add_bos=False) + [fim["suf"]] + \
+                    t.encode(d.get("input_suffix", ""), add_bos=False) + [fim["mid"]]
+                d["prompt"] = ([t.bos_id] if t.add_bos else []) + ids
+                return await self.completion(d, writer)
             if method == "POST" and path in ("/completion", "/completions", "/v1/completions"):
                 return await self.completion(json.loads(body or b"{}"), writer, openai=path.startswith("/v1"))
             if method == "POST" and path == "/v1/chat/completions":
@@ -178,6 +221,56 @@ class Orchestrator:
         except json.JSONDecodeError as e:
             await self._json(writer, {"error": f"invalid JSON: {e}"}, "400 Bad Request")
             return True
+
+    async def slot_action(self, path: str, d: dict, writer) -> bool:
+        """`POST /slots/{id}?action=save|restore|erase` (`tools/server/server.cpp:196-197`): KV state of an idle slot to / from a
+        session file under --slot-save-path (utils/session.py)."""
+        from ..utils import session
+        try:
+            idx = int(path.split("/")[2])
+            slot = self.sched.slots[idx]
+        except (ValueError, IndexError):
+            await self._json(writer, {"error": "no such slot"}, "404 Not Found")
+            return True
+        action = self._query.get("action", "")
+        if action in ("save", "restore") and not self.slot_save_path:
+            await self._json(writer, {"error": "start the server with --slot-save-path"}, "501 Not Implemented")
+            return True
+        fname = os.path.basename(str(d.get("filename", f"slot{idx}.bin")))
+        fpath = os.path.join(self.slot_save_path or "", fname)
+
+        def job(eng):
+            if slot.state.name != "IDLE":
+                raise RuntimeError("slot is busy")
+            if action == "erase":
+                n = len(slot.cache_tokens)
+                if slot.sid is not None:
+                    eng.truncate_seq(slot.sid, 0)
+                slot.cache_tokens, slot.n_past = [], 0
+                return {"id_slot": idx, "n_erased": n}
+            if action == "save":
+                if slot.sid is None:
+                    raise RuntimeError("slot is empty")
+                nbytes = session.save_sequence(eng, slot.sid, fpath, slot.cache_tokens)
+                return {"id_slot": idx, "filename": fname, "n_saved": len(slot.cache_tokens), "n_written": nbytes}
+            if action == "restore":
+                if slot.sid is None:
+                    slot.sid = eng.alloc_seq()
+                hdr = session.load_sequence(eng, slot.sid, fpath)
+                slot.cache_tokens = list(hdr.get("tokens") or [])[: hdr["n_tokens"]]
+                slot.n_past = len(slot.cache_tokens)
+                if slot.n_past != hdr["n_tokens"]:          # no token ids in the file: the cache cannot be matched to prompts
+                    eng.truncate_seq(slot.sid, 0)
+                    slot.cache_tokens, slot.n_past = [], 0
+                return {"id_slot": idx, "filename": fname, "n_restored": slot.n_past}
+            raise ValueError("action must be save, restore or erase")
+        try:
+            res = await asyncio.get_running_loop().run_in_executor(None, self.sched.run_on_engine, job)
+        except (RuntimeError, ValueError, OSError) as e:
+            await self._json(writer, {"error": str(e)}, "400 Bad Request")
+            return True
+        await self._json(writer, res)
+        return True
 
     # ---- static files (ServeDir fallback) -----------------------------------------------------------------
     async def static(self, path: str, writer, head=False) -> bool:
@@ -384,10 +477,16 @@ def main(argv=None):
     ap.add_argument("-b", "--batch-size", type=int, default=2048)
     ap.add_argument("--device", default="cuda")
     ap.add_argument("--static", default=STATIC_DIR)
+    ap.add_argument("--lora", default=os.environ.get("DLP_ARG_LORA"), help="comma separated LoRA adapter GGUFs (path[:scale])")
+    ap.add_argument("--api-key", default=os.environ.get("DLP_API_KEY"), help="require 'Authorization: Bearer <key>' on API routes")
+    ap.add_argument("--max-queue", type=int, default=0, help="answer 503 once this many requests are waiting (0 = unbounded)")
+    ap.add_argument("--slot-save-path", default=None, help="directory for /slots/{id}?action=save|restore files")
+    ap.add_argument("--context-shift", action="store_true", help="slide the context window instead of stopping at n_ctx")
     a = ap.parse_args(argv)
     sched, info, logs = build_service(a.model, a.device, a.ctx_size, a.parallel, a.batch_size, lora=lora_from_args(a))
+    sched.context_shift = a.context_shift
     sched.start()
-    orch = Orchestrator(sched, info, a.static, a.predict, logs)
+    orch = Orchestrator(sched, info, a.static, a.predict, logs, api_key=a.api_key, max_queue=a.max_queue, slot_save_path=a.slot_save_path)
     print(f"dlp_b200 orchestrator ready: http://localhost:{a.port}", flush=True)
     try:
         asyncio.run(orch.serve(a.host, a.port))

@@ -3,7 +3,7 @@
 Parity: default chain order of the reference (`llama.cpp/common/common.h:201-210`, `common/sampling.cpp:179-311`):
 penalties -> top-k -> top-p -> min-p -> temperature -> dist.  Implemented samplers: repetition/frequency/presence
 penalties (`llama-sampling.cpp:2777`), top-k (`:1348`), top-p (`:1543`), min-p (`:1704`), typical (`:1814`),
-temperature (`:1918`), dynamic temperature (`temp_ext :2115`), XTC (`:2222`), mirostat v2 (`:2445`), top-n-sigma (`:2876`),
+DRY (`:3216`), temperature (`:1918`), dynamic temperature (`temp_ext :2115`), XTC (`:2222`), mirostat v2 (`:2445`), top-n-sigma (`:2876`),
 grammar (`:2625`, see grammar.py), greedy (`:1011`), seeded multinomial (`:1255`), logit bias (`:3455`).
 """
 from __future__ import annotations
@@ -34,6 +34,11 @@ class SamplingParams:
     mirostat: int = 0                  # 2 = mirostat v2 (replaces top-k/top-p/min-p)
     mirostat_tau: float = 5.0
     mirostat_eta: float = 0.1
+    dry_multiplier: float = 0.0        # DRY ("don't repeat yourself"): penalty = multiplier * base^(match_len - allowed_length)
+    dry_base: float = 1.75
+    dry_allowed_length: int = 2
+    dry_penalty_last_n: int = -1       # -1 = whole history
+    dry_breakers: tuple = ()           # token ids that end a repeated span (the reference's sequence breakers, tokenised)
     grammar: str = ""                  # GBNF text; "" = unconstrained
     json_schema: dict | None = None    # converted to GBNF when `grammar` is empty
 
@@ -42,7 +47,7 @@ class SamplingParams:
         """True when the chain needs a sampler the device kernel does not implement."""
         return bool(self.repeat_penalty != 1.0 or self.frequency_penalty or self.presence_penalty or self.logit_bias
                     or self.typical_p < 1.0 or self.top_n_sigma > 0 or self.dynatemp_range > 0 or self.xtc_probability > 0
-                    or self.mirostat or self.grammar or self.json_schema is not None)
+                    or self.mirostat or self.grammar or self.json_schema is not None or self.dry_multiplier > 0)
 
     @property
     def greedy(self) -> bool:
@@ -60,6 +65,35 @@ def apply_penalties(logits: torch.Tensor, history: list[int], p: SamplingParams)
     vals = vals - counts.float() * p.frequency_penalty - p.presence_penalty
     logits[ids] = vals
     return logits
+
+
+def apply_dry(logits: torch.Tensor, history: list[int], p: SamplingParams) -> torch.Tensor:
+    """DRY sampler (`llama-sampling.cpp:3216`): a token that would extend a span already present in the history by a match of
+    length n >= allowed_length is penalised by multiplier * base^(n - allowed_length)."""
+    if p.dry_multiplier <= 0 or len(history) < 2:
+        return logits
+    h = history if p.dry_penalty_last_n < 0 else history[-p.dry_penalty_last_n:]
+    last = h[-1]
+    if last in p.dry_breakers:
+        return logits
+    best: dict[int, int] = {}
+    L = len(h)
+    for i in range(L - 2, -1, -1):
+        if h[i] != last:
+            continue
+        n = 1                                   # length of the common suffix of h[:i+1] and h
+        while i - n >= 0 and n < 50 and h[i - n] == h[L - 1 - n] and h[i - n] not in p.dry_breakers:
+            n += 1
+        nxt = h[i + 1]
+        if n > best.get(nxt, 0):
+            best[nxt] = n
+    out = None
+    for tok, n in best.items():
+        if n >= p.dry_allowed_length:
+            if out is None:
+                out = logits.clone()
+            out[tok] -= p.dry_multiplier * p.dry_base ** (n - p.dry_allowed_length)
+    return logits if out is None else out
 
 
 def filter_candidates(logits: torch.Tensor, top_k: int, top_p: float, min_p: float, typical_p: float = 1.0):
@@ -171,6 +205,7 @@ class Sampler:
         for tid, bias in p.logit_bias.items():
             row[tid] += bias
         row = apply_penalties(row, self.history, p)
+        row = apply_dry(row, self.history, p)
         tok = self._pick(row)
         if self.constraint is not None and not self.constraint.allowed(tok):
             # the unconstrained pick breaks the grammar: mask the whole vocabulary and pick again (the reference checks

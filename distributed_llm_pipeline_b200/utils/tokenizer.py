@@ -50,6 +50,7 @@ class Tokenizer:
         self.eos_id = int(meta.get("tokenizer.ggml.eos_token_id", 2))
         self.unk_id = int(meta.get("tokenizer.ggml.unknown_token_id", 0))
         self.eot_id = meta.get("tokenizer.ggml.eot_token_id")
+        self.meta_ids = {k: meta.get(f"tokenizer.ggml.fim_{k}_token_id") for k in ("pre", "suf", "mid")}
         self.add_bos = bool(meta.get("tokenizer.ggml.add_bos_token", self.model == "llama"))
         self.add_space_prefix = bool(meta.get("tokenizer.ggml.add_space_prefix", True))
         self.tok2id = {t: i for i, t in enumerate(self.tokens)}
@@ -190,6 +191,19 @@ class Tokenizer:
                 return bytes([int(t[3:5], 16)])
             return t.replace(SPM_SPACE, " ").encode("utf-8")
         return bytes(self.u2b.get(ch, ord("?")) for ch in t)
+
+    def fim_ids(self) -> dict | None:
+        """Fill-in-the-middle token ids (`tokenizer.ggml.fim_{pre,suf,mid}_token_id`, or the usual spellings in the vocab)."""
+        out = {}
+        for key, names in (("pre", ("<|fim_prefix|>", "<fim_prefix>", "<PRE>", "▁<PRE>")), ("suf", ("<|fim_suffix|>", "<fim_suffix>", "<SUF>", "▁<SUF>")),
+                           ("mid", ("<|fim_middle|>", "<fim_middle>", "<MID>", "▁<MID>"))):
+            tid = self.meta_ids.get(key)
+            if tid is None:
+                tid = next((self.special[n] for n in names if n in self.special), None)
+            if tid is None:
+                return None
+            out[key] = int(tid)
+        return out
 
     def token_texts(self) -> list[str | None]:
         """Text of every token for grammar matching: None for control tokens and for byte fragments that are not valid

@@ -199,3 +199,56 @@ def test_context_shift_keeps_generating_past_n_ctx(tmp_models):
                        n_keep=-1, on_event=lambda k, c: logs.append(c) if k == "log" else None)
     assert len(r.output_ids) == 70 and any("context shift" in x for x in logs)
     assert sched.metrics.c["context_shifts_total"] >= 1
+
+
+def _serve(orch):
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    port = s.getsockname()[1]
+    s.close()
+    loop = asyncio.new_event_loop()
+    threading.Thread(target=lambda: loop.run_until_complete(orch.serve("127.0.0.1", port)), daemon=True).start()
+    for _ in range(100):
+        try:
+            socket.create_connection(("127.0.0.1", port), timeout=0.2).close()
+            break
+        except OSError:
+            time.sleep(0.05)
+    return port
+
+
+def test_api_key_slot_save_restore_and_templates(tmp_models, tmp_path):
+    from distributed_llm_pipeline_b200.serving.orchestrator import apply_chat_template
+    sched, info, logs = build_service(tmp_models[("tiny", "F16")], device="cpu", n_ctx=128, n_slots=1, n_batch=32)
+    sched.start()
+    port = _serve(Orchestrator(sched, info, n_predict=8, startup_logs=logs, api_key="s3cret", slot_save_path=str(tmp_path)))
+    try:
+        body = json.dumps({"prompt": "a b c d e f", "n_predict": 4, "temperature": 0}).encode()
+        st, _, _ = _http(port, "POST", "/completion", body)
+        assert " 401 " in st
+        st, _, _ = _http(port, "GET", "/health")
+        assert " 200 " in st
+        auth = {"Authorization": "Bearer s3cret"}
+        _, _, out = _http(port, "POST", "/completion", body, auth)
+        first = json.loads(out)["content"]
+        _, _, out = _http(port, "POST", "/slots/0?action=save", json.dumps({"filename": "s.bin"}).encode(), auth)
+        saved = json.loads(out)
+        assert saved["n_saved"] > 0 and (tmp_path / "s.bin").exists()
+        _, _, out = _http(port, "POST", "/slots/0?action=erase", b"{}", auth)
+        assert json.loads(out)["n_erased"] == saved["n_saved"]
+        _, _, out = _http(port, "POST", "/slots/0?action=restore", json.dumps({"filename": "s.bin"}).encode(), auth)
+        assert json.loads(out)["n_restored"] == saved["n_saved"]
+        _, _, out = _http(port, "POST", "/completion", body, auth)       # served from the restored cache: same text, prefix reused
+        d = json.loads(out)
+        assert d["content"] == first and d["timings"]["cache_n"] > 0
+        _, _, out = _http(port, "POST", "/apply-template", json.dumps({"messages": [{"role": "user", "content": "hi"}]}).encode(), auth)
+        assert json.loads(out)["prompt"] == "hi"
+        st, _, _ = _http(port, "POST", "/infill", json.dumps({"input_prefix": "a", "input_suffix": "b"}).encode(), auth)
+        assert " 501 " in st                                             # synthetic vocab has no FIM tokens
+    finally:
+        sched.stop()
+    msgs = [{"role": "system", "content": "S"}, {"role": "user", "content": "U"}]
+    assert apply_chat_template({"tokenizer.chat_template": "<|im_start|>"}, msgs).endswith("<|im_start|>assistant\n")
+    assert apply_chat_template({"tokenizer.chat_template": "[INST] <<SYS>>"}, msgs) == "[INST] <<SYS>>\nS\n<</SYS>>\n\nU [/INST]"
+    assert "<start_of_turn>model" in apply_chat_template({"tokenizer.chat_template": "<start_of_turn>"}, msgs)
+    assert apply_chat_template({"tokenizer.chat_template": "<|start_header_id|>"}, msgs).count("<|eot_id|>") == 2

@@ -143,3 +143,25 @@ def test_copy_seq_and_context_shift(tmp_models, key):
     assert nmse(k0_fresh, k0) < 1e-5
     nxt = eng.decode([a], [9], sample=False)[0]             # and decoding continues from position 14
     assert torch.isfinite(nxt).all() and eng.seq_len(a) == 15
+
+
+def test_yarn_rope_scaling(tmp_path):
+    """YaRN: frequencies below the correction range are interpolated by 1/factor, those above kept; the engine folds the
+    magnitude correction into the pre-scaled Q and matches the oracle."""
+    from distributed_llm_pipeline_b200.gguf import write_synthetic_gguf
+    from distributed_llm_pipeline_b200.models.reference import rope_attn_scale
+    cfg = preset("tiny", yarn_factor=4.0, yarn_orig_ctx=128, n_ctx_train=512)
+    inv = rope_inv_freq(cfg)
+    base = rope_inv_freq(preset("tiny"))
+    assert torch.allclose(inv[0], base[0]) and torch.allclose(inv[-1], base[-1] / 4.0)     # extrapolated ... interpolated
+    assert ((inv <= base * 1.0001) & (inv >= base / 4.0001)).all() and rope_attn_scale(cfg) > 1.0
+    path = write_synthetic_gguf(str(tmp_path / "yarn.gguf"), cfg, "F16", seed=2)
+    ref = ReferenceModel.from_gguf(path)
+    assert ref.cfg.yarn_factor == 4.0 and ref.cfg.yarn_orig_ctx == 128
+    prompt = list(range(5, 45))
+    want = ref.forward(prompt, ref.new_cache(64))[-1]
+    eng = LlamaEngine(load_weights(path, "cpu"), n_ctx=64, max_seqs=1, page_size=16, max_batch_tokens=64)
+    got = eng.prefill(eng.alloc_seq(), prompt)
+    assert nmse(want, got.float().flatten()) < 1e-5
+    plain = ReferenceModel.from_gguf(write_synthetic_gguf(str(tmp_path / "plain.gguf"), preset("tiny"), "F16", seed=2))
+    assert nmse(plain.forward(prompt, plain.new_cache(64))[-1], want) > 1e-4             # and it is not a no-op

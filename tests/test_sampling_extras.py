@@ -114,3 +114,32 @@ def test_embed_pooling(tmp_models):
     h = ref.forward(ids, ref.new_cache(16), return_hidden=True)
     want = rms_norm(h, ref.w["output_norm.weight"], ref.cfg.rms_eps)
     assert torch.allclose(allv, want, atol=2e-3, rtol=2e-3)
+
+
+def test_dry_sampler_penalises_repeated_spans():
+    from distributed_llm_pipeline_b200.serving.sampler import apply_dry
+    p = SamplingParams(dry_multiplier=1.0, dry_base=2.0, dry_allowed_length=2)
+    hist = [5, 6, 7, 8, 1, 5, 6, 7]                 # "... 5 6 7" seen before, followed by 8
+    logits = torch.zeros(10)
+    out = apply_dry(logits, hist, p)
+    assert out[8] == -2.0 and (out[torch.arange(10) != 8] == 0).all()     # match length 3: 1.0 * 2^(3-2)
+    assert torch.equal(apply_dry(logits, [1, 2, 3, 4], p), logits)        # no repetition: untouched
+    pb = SamplingParams(dry_multiplier=1.0, dry_base=2.0, dry_allowed_length=2, dry_breakers=(6,))
+    assert torch.equal(apply_dry(logits, hist, pb), logits)               # the breaker cuts the match to length 1
+    s = Sampler(SamplingParams(temperature=0.0, dry_multiplier=5.0))
+    s.history = list(hist)
+    lg = torch.zeros(10)
+    lg[8], lg[3] = 1.0, 0.5
+    assert s.sample(lg) == 3
+
+
+def test_eval_callback_and_memory_breakdown(tmp_models):
+    eng = _engine(tmp_models[("tiny", "F16")])
+    seen = []
+    eng.eval_callback = lambda name, il, t: seen.append((name, il, tuple(t.shape)))
+    sid = eng.alloc_seq()
+    eng.prefill(sid, [1, 2, 3])
+    eng.decode([sid], [4], sample=False)
+    assert seen == [("l_out", 0, (3, 256)), ("l_out", 1, (3, 256)), ("l_out", 0, (1, 256)), ("l_out", 1, (1, 256))]
+    mb = eng.memory_breakdown()
+    assert mb["model"] > 0 and mb["kv_cache"] > 0 and mb["compute"] > 0
