@@ -106,7 +106,8 @@ def row_bytes(ggml_type: GGMLType, n_elements: int) -> int:
 
 
 # File-type ids written to general.file_type (llama_ftype); only those we emit.
-FTYPE = {"F32": 0, "F16": 1, "Q8_0": 7, "Q4_K_M": 15, "Q5_K_M": 17, "Q6_K": 18, "BF16": 32}
+FTYPE = {"F32": 0, "F16": 1, "Q4_0": 2, "Q4_1": 3, "Q8_0": 7, "Q5_0": 8, "Q5_1": 9, "Q2_K": 10, "Q3_K": 12, "Q4_K_M": 15,
+         "Q5_K_M": 17, "Q6_K": 18, "BF16": 32}
 
 
 class TokenType(enum.IntEnum):

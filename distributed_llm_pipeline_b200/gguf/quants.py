@@ -97,6 +97,72 @@ def dequant_q4_0(raw: np.ndarray) -> np.ndarray:
     return (d[:, None] * q).reshape(-1)
 
 
+def dequant_q4_1(raw: np.ndarray) -> np.ndarray:
+    b = _blocks(raw, GGMLType.Q4_1)
+    d, m = _f16(b[:, 0:2]), _f16(b[:, 2:4])
+    qs = b[:, 4:]
+    q = np.concatenate([qs & 0x0F, qs >> 4], axis=1).astype(np.float32)
+    return (d[:, None] * q + m[:, None]).reshape(-1)
+
+
+def _q5_high_bits(qh_bytes: np.ndarray) -> np.ndarray:
+    """[nb, 4] bytes -> [nb, 32] fifth bits (bit j of the little-endian u32 belongs to element j)."""
+    qh = qh_bytes.copy().view("<u4").reshape(-1)
+    return ((qh[:, None] >> np.arange(32, dtype=np.uint32)[None, :]) & 1).astype(np.uint8)
+
+
+def dequant_q5_0(raw: np.ndarray) -> np.ndarray:
+    b = _blocks(raw, GGMLType.Q5_0)
+    d = _f16(b[:, 0:2])
+    hb = _q5_high_bits(b[:, 2:6])
+    qs = b[:, 6:]
+    q = np.concatenate([qs & 0x0F, qs >> 4], axis=1) | (hb << 4)
+    return (d[:, None] * (q.astype(np.float32) - 16.0)).reshape(-1)
+
+
+def dequant_q5_1(raw: np.ndarray) -> np.ndarray:
+    b = _blocks(raw, GGMLType.Q5_1)
+    d, m = _f16(b[:, 0:2]), _f16(b[:, 2:4])
+    hb = _q5_high_bits(b[:, 4:8])
+    qs = b[:, 8:]
+    q = np.concatenate([qs & 0x0F, qs >> 4], axis=1) | (hb << 4)
+    return (d[:, None] * q.astype(np.float32) + m[:, None]).reshape(-1)
+
+
+def dequant_q2_k(raw: np.ndarray) -> np.ndarray:
+    """block_q2_K: scales[16] (4-bit scale | 4-bit min << 4), qs[64] (2 bits), d, dmin  (ggml-common.h, dequantize_row_q2_K)."""
+    b = _blocks(raw, GGMLType.Q2_K)
+    nb = b.shape[0]
+    sc = b[:, 0:16]
+    qs = b[:, 16:80].reshape(nb, 2, 32)                                  # two 128-element halves, 32 bytes each
+    d, dmin = _f16(b[:, 80:82]), _f16(b[:, 82:84])
+    shifts = np.array([0, 2, 4, 6], np.uint8)
+    q = ((qs[:, :, None, :] >> shifts[None, None, :, None]) & 3).astype(np.float32)   # [nb, half, shift, 32]
+    q = q.reshape(nb, 16, 16)                                            # 16 sub-blocks of 16 in element order
+    dl = d[:, None] * (sc & 0x0F).astype(np.float32)
+    ml = dmin[:, None] * (sc >> 4).astype(np.float32)
+    return (dl[:, :, None] * q - ml[:, :, None]).reshape(-1)
+
+
+def dequant_q3_k(raw: np.ndarray) -> np.ndarray:
+    """block_q3_K: hmask[32], qs[64] (low 2 bits), scales[12] (16 x 6-bit), d  (dequantize_row_q3_K)."""
+    b = _blocks(raw, GGMLType.Q3_K)
+    nb = b.shape[0]
+    hmask = b[:, 0:32]
+    qs = b[:, 32:96].reshape(nb, 2, 32)
+    s12 = b[:, 96:108]
+    d = _f16(b[:, 108:110])
+    lo4 = np.concatenate([s12[:, 0:8] & 0x0F, s12[:, 0:8] >> 4], axis=1)                      # scales 0..15, low 4 bits
+    hi2 = np.concatenate([(s12[:, 8:12] >> s) & 3 for s in (0, 2, 4, 6)], axis=1)             # scales 0..15, high 2 bits
+    scales = (lo4 | (hi2 << 4)).astype(np.int8).astype(np.float32) - 32.0
+    shifts = np.array([0, 2, 4, 6], np.uint8)
+    low = ((qs[:, :, None, :] >> shifts[None, None, :, None]) & 3).astype(np.int8)            # [nb, half, shift, 32]
+    bit = np.arange(8, dtype=np.uint8).reshape(1, 2, 4, 1)                                    # mask bit = half*4 + shift
+    high = ((hmask[:, None, None, :] >> bit) & 1).astype(np.int8)
+    q = (low - 4 * (1 - high)).astype(np.float32).reshape(nb, 16, 16)
+    return (d[:, None, None] * scales[:, :, None] * q).reshape(-1)
+
+
 def dequant_q4_k(raw: np.ndarray) -> np.ndarray:
     b = _blocks(raw, GGMLType.Q4_K)
     d = _f16(b[:, 0:2])
@@ -161,6 +227,16 @@ def dequantize(raw: np.ndarray, ggml_type: GGMLType, shape: tuple[int, ...] | No
         out = dequant_q8_0(raw)
     elif t == GGMLType.Q4_0:
         out = dequant_q4_0(raw)
+    elif t == GGMLType.Q4_1:
+        out = dequant_q4_1(raw)
+    elif t == GGMLType.Q5_0:
+        out = dequant_q5_0(raw)
+    elif t == GGMLType.Q5_1:
+        out = dequant_q5_1(raw)
+    elif t == GGMLType.Q2_K:
+        out = dequant_q2_k(raw)
+    elif t == GGMLType.Q3_K:
+        out = dequant_q3_k(raw)
     elif t == GGMLType.Q4_K:
         out = dequant_q4_k(raw)
     elif t == GGMLType.Q5_K:
@@ -183,9 +259,9 @@ def _nearest_int(x: np.ndarray) -> np.ndarray:
 def quant_q8_0(x: np.ndarray) -> np.ndarray:
     x = np.ascontiguousarray(x, dtype=np.float32).reshape(-1, 32)
     amax = np.abs(x).max(axis=1)
-    d = (amax / 127.0).astype(np.float16)
-    df = d.astype(np.float32)
-    inv = np.where(df > 0, 1.0 / np.where(df > 0, df, 1.0), 0.0)
+    df = (amax / np.float32(127.0)).astype(np.float32)            # the inverse uses the unrounded scale (quantize_row_q8_0_ref)
+    d = df.astype(np.float16)
+    inv = np.where(df > 0, np.float32(1.0) / np.where(df > 0, df, np.float32(1.0)), np.float32(0.0)).astype(np.float32)
     q = np.clip(_nearest_int(x * inv[:, None]), -127, 127).astype(np.int8)
     out = np.empty((x.shape[0], 34), np.uint8)
     out[:, 0:2] = d.view(np.uint8).reshape(-1, 2)
@@ -197,13 +273,109 @@ def quant_q4_0(x: np.ndarray) -> np.ndarray:
     x = np.ascontiguousarray(x, dtype=np.float32).reshape(-1, 32)
     idx = np.abs(x).argmax(axis=1)
     mx = x[np.arange(x.shape[0]), idx]
-    d = (mx / -8.0).astype(np.float16)
-    df = d.astype(np.float32)
-    inv = np.where(df != 0, 1.0 / np.where(df != 0, df, 1.0), 0.0)
-    q = np.clip(_nearest_int(x * inv[:, None] + 8.0), 0, 15).astype(np.uint8)
+    df = (mx / np.float32(-8.0)).astype(np.float32)
+    d = df.astype(np.float16)
+    inv = np.where(df != 0, np.float32(1.0) / np.where(df != 0, df, np.float32(1.0)), np.float32(0.0)).astype(np.float32)
+    q = np.clip(np.trunc(x * inv[:, None] + 8.5), 0, 15).astype(np.uint8)      # (int8)(x/d + 8.5), as quantize_row_q4_0_ref
     out = np.empty((x.shape[0], 18), np.uint8)
     out[:, 0:2] = d.view(np.uint8).reshape(-1, 2)
     out[:, 2:] = q[:, :16] | (q[:, 16:] << 4)
+    return out.reshape(-1)
+
+
+def quant_q4_1(x: np.ndarray) -> np.ndarray:
+    x = np.ascontiguousarray(x, dtype=np.float32).reshape(-1, 32)
+    mn, mx = x.min(axis=1), x.max(axis=1)
+    d = (mx - mn) / 15.0
+    inv = np.where(d != 0, 1.0 / np.where(d != 0, d, 1.0), 0.0).astype(np.float32)
+    q = np.clip(np.trunc((x - mn[:, None]) * inv[:, None] + 0.5), 0, 15).astype(np.uint8)
+    out = np.empty((x.shape[0], 20), np.uint8)
+    out[:, 0:2] = d.astype(np.float16).view(np.uint8).reshape(-1, 2)
+    out[:, 2:4] = mn.astype(np.float16).view(np.uint8).reshape(-1, 2)
+    out[:, 4:] = q[:, :16] | (q[:, 16:] << 4)
+    return out.reshape(-1)
+
+
+def _pack_q5(q: np.ndarray):
+    """5-bit values [nb, 32] -> (qh [nb, 4] bytes, qs [nb, 16] nibbles)."""
+    hb = (q >> 4).astype(np.uint32)
+    qh = (hb << np.arange(32, dtype=np.uint32)[None, :]).sum(axis=1, dtype=np.uint64).astype("<u4")
+    lo = (q & 0x0F).astype(np.uint8)
+    return qh.view(np.uint8).reshape(-1, 4), lo[:, :16] | (lo[:, 16:] << 4)
+
+
+def quant_q5_0(x: np.ndarray) -> np.ndarray:
+    x = np.ascontiguousarray(x, dtype=np.float32).reshape(-1, 32)
+    idx = np.abs(x).argmax(axis=1)
+    mx = x[np.arange(x.shape[0]), idx]
+    d = mx / -16.0
+    inv = np.where(d != 0, 1.0 / np.where(d != 0, d, 1.0), 0.0).astype(np.float32)
+    q = np.clip(np.trunc(x * inv[:, None] + 16.5), 0, 31).astype(np.uint8)
+    out = np.empty((x.shape[0], 22), np.uint8)
+    out[:, 0:2] = d.astype(np.float16).view(np.uint8).reshape(-1, 2)
+    out[:, 2:6], out[:, 6:] = _pack_q5(q)
+    return out.reshape(-1)
+
+
+def quant_q5_1(x: np.ndarray) -> np.ndarray:
+    x = np.ascontiguousarray(x, dtype=np.float32).reshape(-1, 32)
+    mn, mx = x.min(axis=1), x.max(axis=1)
+    d = (mx - mn) / 31.0
+    inv = np.where(d != 0, 1.0 / np.where(d != 0, d, 1.0), 0.0).astype(np.float32)
+    q = np.clip(np.trunc((x - mn[:, None]) * inv[:, None] + 0.5), 0, 31).astype(np.uint8)
+    out = np.empty((x.shape[0], 24), np.uint8)
+    out[:, 0:2] = d.astype(np.float16).view(np.uint8).reshape(-1, 2)
+    out[:, 2:4] = mn.astype(np.float16).view(np.uint8).reshape(-1, 2)
+    out[:, 4:8], out[:, 8:] = _pack_q5(q)
+    return out.reshape(-1)
+
+
+def quant_q2_k(x: np.ndarray) -> np.ndarray:
+    """Closed-form Q2_K encoder (per 16-element sub-block affine fit, 4-bit scale / min; no search)."""
+    x = np.ascontiguousarray(x, dtype=np.float32).reshape(-1, 16, 16)
+    nb = x.shape[0]
+    mn = np.minimum(x.min(axis=2), 0.0)
+    scale = (x.max(axis=2) - mn) / 3.0
+    d = scale.max(axis=1) / 15.0
+    dmin = (-mn).max(axis=1) / 15.0
+    d16, dmin16 = d.astype(np.float16).astype(np.float32), dmin.astype(np.float16).astype(np.float32)
+    sc = np.clip(_nearest_int(scale / np.where(d16 > 0, d16, 1.0)[:, None]), 0, 15) * (d16 > 0)[:, None]
+    m = np.clip(_nearest_int(-mn / np.where(dmin16 > 0, dmin16, 1.0)[:, None]), 0, 15) * (dmin16 > 0)[:, None]
+    dl, ml = d16[:, None] * sc, dmin16[:, None] * m
+    q = np.clip(_nearest_int((x + ml[:, :, None]) / np.where(dl > 0, dl, 1.0)[:, :, None]), 0, 3).astype(np.uint8) * (dl > 0)[:, :, None].astype(np.uint8)
+    out = np.empty((nb, 84), np.uint8)
+    out[:, 0:16] = (sc | (m << 4)).astype(np.uint8)
+    q4 = q.reshape(nb, 2, 4, 32)                                          # [half, shift, 32]
+    out[:, 16:80] = (q4[:, :, 0] | (q4[:, :, 1] << 2) | (q4[:, :, 2] << 4) | (q4[:, :, 3] << 6)).reshape(nb, 64)
+    out[:, 80:82] = d.astype(np.float16).view(np.uint8).reshape(-1, 2)
+    out[:, 82:84] = dmin.astype(np.float16).view(np.uint8).reshape(-1, 2)
+    return out.reshape(-1)
+
+
+def quant_q3_k(x: np.ndarray) -> np.ndarray:
+    """Closed-form Q3_K encoder (symmetric 3-bit per 16-element sub-block, 6-bit scales)."""
+    x = np.ascontiguousarray(x, dtype=np.float32).reshape(-1, 16, 16)
+    nb = x.shape[0]
+    idx = np.abs(x).argmax(axis=2)
+    mx = np.take_along_axis(x, idx[:, :, None], axis=2)[:, :, 0]
+    scale = mx / -4.0                                                     # value = scale * q, q in [-4, 3]
+    amax_s = np.abs(scale).max(axis=1)
+    d = amax_s / 31.0
+    d16 = d.astype(np.float16).astype(np.float32)
+    ls = np.clip(_nearest_int(scale / np.where(d16 > 0, d16, 1.0)[:, None]), -32, 31) * (d16 > 0)[:, None]
+    eff = d16[:, None] * ls
+    q = np.clip(_nearest_int(x / np.where(eff != 0, eff, 1.0)[:, :, None]), -4, 3) * (eff != 0)[:, :, None]
+    u = (q + 4).astype(np.uint8)                                          # 0..7
+    low, high = (u & 3).reshape(nb, 2, 4, 32), (u >> 2).reshape(nb, 2, 4, 32)
+    out = np.zeros((nb, 110), np.uint8)
+    bit = np.arange(8, dtype=np.uint8).reshape(1, 2, 4, 1)
+    out[:, 0:32] = (high << bit).sum(axis=(1, 2)).astype(np.uint8)
+    out[:, 32:96] = (low[:, :, 0] | (low[:, :, 1] << 2) | (low[:, :, 2] << 4) | (low[:, :, 3] << 6)).reshape(nb, 64)
+    l6 = (ls + 32).astype(np.uint8)
+    out[:, 96:104] = (l6[:, 0:8] & 0x0F) | ((l6[:, 8:16] & 0x0F) << 4)
+    h2 = l6 >> 4
+    out[:, 104:108] = h2[:, 0:4] | (h2[:, 4:8] << 2) | (h2[:, 8:12] << 4) | (h2[:, 12:16] << 6)
+    out[:, 108:110] = d.astype(np.float16).view(np.uint8).reshape(-1, 2)
     return out.reshape(-1)
 
 
@@ -314,6 +486,11 @@ def quantize(x: np.ndarray, ggml_type: GGMLType) -> np.ndarray:
     fn = {
         GGMLType.Q8_0: quant_q8_0,
         GGMLType.Q4_0: quant_q4_0,
+        GGMLType.Q4_1: quant_q4_1,
+        GGMLType.Q5_0: quant_q5_0,
+        GGMLType.Q5_1: quant_q5_1,
+        GGMLType.Q2_K: quant_q2_k,
+        GGMLType.Q3_K: quant_q3_k,
         GGMLType.Q4_K: quant_q4_k,
         GGMLType.Q5_K: quant_q5_k,
         GGMLType.Q6_K: quant_q6_k,

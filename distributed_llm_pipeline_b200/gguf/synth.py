@@ -41,6 +41,10 @@ def tensor_type_for(name: str, ftype: str, i_layer: int, cfg: ModelConfig) -> GG
         return GGMLType.Q8_0
     if ftype == "Q6_K":
         return GGMLType.Q6_K
+    if ftype in ("Q4_0", "Q4_1", "Q5_0", "Q5_1"):      # legacy block types: uniform (decoded to fp16 at load by the engine)
+        return GGMLType[ftype]
+    if ftype in ("Q2_K", "Q3_K"):                      # low-bit K types keep the output matrix at Q6_K like the reference
+        return GGMLType.Q6_K if name == "output.weight" else GGMLType[ftype]
     if ftype in ("Q4_K_M", "Q5_K_M"):
         base = GGMLType.Q4_K if ftype == "Q4_K_M" else GGMLType.Q5_K
         if name == "output.weight":

@@ -11,7 +11,8 @@ gguf = pytest.importorskip("gguf")
 from gguf import quants as GQ  # noqa: E402
 
 TYPES = [(GGMLType.Q8_0, 3e-5), (GGMLType.Q4_0, 1e-2), (GGMLType.Q4_K, 1e-2), (GGMLType.Q5_K, 3e-3), (GGMLType.Q6_K, 1e-3),
-         (GGMLType.F16, 1e-6), (GGMLType.BF16, 1e-4)]
+         (GGMLType.F16, 1e-6), (GGMLType.BF16, 1e-4), (GGMLType.Q4_1, 1e-2), (GGMLType.Q5_0, 3e-3), (GGMLType.Q5_1, 3e-3),
+         (GGMLType.Q2_K, 0.2), (GGMLType.Q3_K, 5e-2)]
 
 
 @pytest.mark.parametrize("t,tol", TYPES)
@@ -24,6 +25,27 @@ def test_quant_roundtrip_matches_gguf_py(t, tol):
     assert np.array_equal(mine, ref.reshape(x.shape))          # bit-exact decode
     nmse = ((mine - x) ** 2).sum() / (x ** 2).sum()
     assert nmse < tol
+
+
+@pytest.mark.parametrize("t", [GGMLType.Q4_0, GGMLType.Q4_1, GGMLType.Q5_0, GGMLType.Q5_1, GGMLType.Q8_0])
+def test_legacy_encoders_are_bit_exact_with_gguf_py(t):
+    rng = np.random.default_rng(3)
+    x = (rng.standard_normal((8, 256)) * 0.05).astype(np.float32)
+    ref = GQ.quantize(x, gguf.GGMLQuantizationType(int(t)))
+    assert np.array_equal(quantize(x, t).reshape(ref.shape), ref)
+
+
+@pytest.mark.parametrize("t,fields", [(GGMLType.Q2_K, [(80, 0.01), (82, 0.02)]), (GGMLType.Q3_K, [(108, 0.01)])])
+def test_low_bit_k_decoders_on_arbitrary_blocks(t, fields):
+    """Every bit pattern of the packed scale / quant fields decodes as gguf-py does (fp16 fields pinned to finite values)."""
+    from distributed_llm_pipeline_b200.gguf.constants import BLOCK_GEOMETRY
+    rng = np.random.default_rng(4)
+    nbytes = BLOCK_GEOMETRY[t][1]
+    raw = rng.integers(0, 256, size=(32, nbytes), dtype=np.uint8)
+    for col, val in fields:
+        raw[:, col:col + 2] = np.array([val], np.float16).view(np.uint8)
+    ref = GQ.dequantize(raw.reshape(1, -1), gguf.GGMLQuantizationType(int(t))).reshape(-1)
+    assert np.allclose(dequantize(raw, t), ref, rtol=0, atol=1e-7)
 
 
 @pytest.mark.parametrize("t", [GGMLType.Q8_0, GGMLType.Q4_K, GGMLType.Q5_K, GGMLType.Q6_K])
@@ -44,7 +66,7 @@ def test_scale_min_pack_roundtrip():
     assert np.array_equal(sc, s2) and np.array_equal(mn, m2)
 
 
-@pytest.mark.parametrize("ftype", ["F16", "Q8_0", "Q4_K_M"])
+@pytest.mark.parametrize("ftype", ["F16", "Q8_0", "Q4_K_M", "Q5_1", "Q3_K"])
 def test_synthetic_file_readable_by_reference_reader(tmp_path, ftype):
     cfg = preset("tiny")
     path = write_synthetic_gguf(str(tmp_path / "m.gguf"), cfg, ftype)
