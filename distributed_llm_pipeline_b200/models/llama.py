@@ -248,10 +248,20 @@ class LlamaEngine:
         small = T <= 4 and not tp  # fused mat-vec path (norm in prologue, residual add in epilogue)
         # --- attention block ---
         if small:
-            qkv = ops.linear(lw.wqkv, h, "f32", norm_w=lw.attn_norm, eps=cfg.rms_eps, out=self.qkv32[:T])
+            qkv = self.qkv32[:T]
+            if lw.wv is None:
+                ops.linear(lw.wqkv, h, "f32", norm_w=lw.attn_norm, eps=cfg.rms_eps, out=qkv)
+            else:   # V in its own block type: second mat-vec into the tail columns
+                ops.linear(lw.wqkv, h, "f32", norm_w=lw.attn_norm, eps=cfg.rms_eps, out=qkv[:, :lw.wqkv.N])
+                ops.linear(lw.wv, h, "f32", norm_w=lw.attn_norm, eps=cfg.rms_eps, out=qkv[:, lw.wqkv.N:])
         else:
             xn = ops.rmsnorm(h, lw.attn_norm, cfg.rms_eps, out=self.xn[:T])
-            qkv = ops.linear(lw.wqkv, xn, "f16", out=self.qkv16[:T], scratch=self._scratch_for(lw.wqkv))
+            qkv = self.qkv16[:T]
+            if lw.wv is None:
+                ops.linear(lw.wqkv, xn, "f16", out=qkv, scratch=self._scratch_for(lw.wqkv))
+            else:
+                ops.linear(lw.wqkv, xn, "f16", out=qkv[:, :lw.wqkv.N], scratch=self._scratch_for(lw.wqkv))
+                ops.linear(lw.wv, xn, "f16", out=qkv[:, lw.wqkv.N:], scratch=self._scratch_for(lw.wv))
         q = self._rope(il, qkv, T)
         att = attn_fn(il, q, T)
         if tp:
