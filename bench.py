@@ -160,6 +160,7 @@ def run_ours(args) -> dict:
     barrier()
     torch.cuda.synchronize()
     n0 = ops.launch_count
+    r0 = getattr(eng, "launches_replayed", 0)
     if rank == 0:
         clocks.start()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -174,8 +175,7 @@ def run_ours(args) -> dict:
     if world > 1:
         dist.all_reduce(t_dec, op=dist.ReduceOp.MAX)
     ms_per_step = t_dec.item() / args.steps
-    per_graph = getattr(eng, "launches_per_graph", {}).get((1, True), 0)
-    launches = per_graph * args.steps + (ops.launch_count - n0)
+    launches = (getattr(eng, "launches_replayed", 0) - r0) + (ops.launch_count - n0)   # inside graph replays + eager
 
     # ---- end to end through the public API: pinned H2D token in, D2H token out, every step ----
     tok_host = torch.zeros(1, dtype=torch.int32).pin_memory()

@@ -7,8 +7,19 @@
 // TP ranks own disjoint KV heads.  One CTA = (split, kv head [x q-head group], query); the G <= 4 query
 // heads that share a KV head are processed together so each K/V byte is read once per group.
 #include "kernels.cuh"
+#include <cooperative_groups.h>
 
 namespace dlp {
+
+__device__ __forceinline__ void cp_async16(void* smem, const void* gmem, bool pred) {
+    const uint32_t s = smem_u32(smem);
+    const int sz = pred ? 16 : 0;  // src-size 0 => zero fill
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(s), "l"(gmem), "r"(sz) : "memory");
+}
+__device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_all;" ::: "memory"); }
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait_group() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
 
 template <int D, int G>
 __global__ void __launch_bounds__(128) attn_decode_kernel(const AttnParams p) {
@@ -22,7 +33,9 @@ __global__ void __launch_bounds__(128) attn_decode_kernel(const AttnParams p) {
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int grp = lane >> 3, sub = lane & 7;
 
+    trace_event(p.trace, TR_ATTN | TR_BEGIN);
     pdl_wait();
+    trace_event(p.trace, TR_ATTN | TR_WAITED);
     const int len = p.kv_len[qi];
     // effective split count grows with the context (one split per 64 keys): a short context is handled by a single CTA
     // that writes the final result itself; the launch shape (n_splits) stays fixed so the step can live in a CUDA graph
@@ -110,6 +123,7 @@ __global__ void __launch_bounds__(128) attn_decode_kernel(const AttnParams p) {
             for (int i = 0; i < NV; ++i) { kr[i] = kn[i]; vr[i] = vn[i]; }
         }
     }
+    trace_event(p.trace, TR_ATTN | TR_MAIN_DONE);
     pdl_launch_dependents();
     // merge the 4 lane groups of the warp, then the 4 warps of the CTA
     __shared__ float sm_m[4][G], sm_l[4][G];
@@ -159,6 +173,7 @@ __global__ void __launch_bounds__(128) attn_decode_kernel(const AttnParams p) {
             if (d == 0) { p.part_ml[pi * 2] = mn; p.part_ml[pi * 2 + 1] = ls; }
         }
     }
+    trace_event(p.trace, TR_ATTN | TR_END);       // (CTA 0 is rarely the combining CTA: its END marks the partial write)
     if (eff == 1 || p.counters == nullptr) return;
     // fused LSE combine: the last split CTA of this (query, kv-head group) to finish merges all partials - no second launch
     __shared__ int is_last;
@@ -187,6 +202,331 @@ __global__ void __launch_bounds__(128) attn_decode_kernel(const AttnParams p) {
         }
         p.out[((size_t)qi * p.Hq + hq0 + g) * D + d] = __float2half_rn(ls > 0.f ? acc / ls : 0.f);
     }
+}
+
+// ---------------------------------------------------------------------------------------------
+// Decode step in ONE launch: RoPE on Q and on the new token's K, paged write of that token's K/V, split-KV attention over the
+// cache, and the split combine through distributed shared memory.
+//
+//   * The splits of one (query, KV-head group) form a thread-block CLUSTER (grid.x = cluster size = n_splits <= 16): partial
+//     (o, m, l) triples are stored straight into the leader CTA's shared memory (st.shared::cluster through
+//     cluster.map_shared_rank) and merged after one cluster barrier - no global workspace, no __threadfence + atomic ticket,
+//     no L2 round trips, no second kernel.
+//   * Q arrives un-rotated as the fp32 output row of the fused QKV mat-vec; every lane rotates the 16 dims it owns (the
+//     half-split "neox" partner dim sits 4 lanes away: one shuffle).  The new token (position kv_len-1) is not in the cache
+//     yet: the CTA that owns the tail of the key range rotates K, writes K/V to the page and folds the token in from
+//     registers, so the separate RoPE + KV-write launch of the unfused path (rope_kv_kernel) disappears from the decode step.
+// Reference counterparts: ggml_rope_ext + ggml_set_rows (K/V cache write) + flash_attn_ext_vec + flash_attn_combine_results -
+// four graph nodes / launches per layer in `llama.cpp/src/models/llama.cpp:60-110`, `ggml-cuda/fattn-vec.cuh`.
+template <int D, int G>
+__global__ void __launch_bounds__(128) attn_decode_rope_kernel(const AttnParams p, const float* __restrict__ qkv,
+                                                               const float* __restrict__ inv_freq,
+                                                               const float2* __restrict__ rope_cs, __half* __restrict__ kc_w,
+                                                               __half* __restrict__ vc_w, int neox, float q_scale) {
+    namespace cg = cooperative_groups;
+    constexpr int DL = D / 8;     // dims per lane (8 lanes share one token)
+    constexpr int NV = DL / 8;    // 16-byte loads per lane and tensor
+    constexpr int MAXS = 16;
+    static_assert(DL % 8 == 0, "head dim must be a multiple of 64");
+    cg::cluster_group cluster = cg::this_cluster();
+    const int split = blockIdx.x;                      // == rank in the cluster (cluster dims = (gridDim.x, 1, 1))
+    const int gqa = p.Hq / p.Hkv;
+    const int groups_per_kv = gqa / G;
+    const int kvh = blockIdx.y / groups_per_kv;
+    const int hq0 = kvh * gqa + (blockIdx.y % groups_per_kv) * G;
+    const int qi = blockIdx.z;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int grp = lane >> 3, sub = lane & 7;
+    const int H = p.Hq + 2 * p.Hkv;
+
+    // (a variant that staged 64-key K/V tiles in 64 KB of dynamic shared memory with cp.async measured slower: the large
+    // carve-out keeps the kernel from sharing an SM with the neighbouring mat-vecs and costs the PDL overlap)
+    __shared__ float sm_m[4][G], sm_l[4][G];
+    __shared__ float sm_o[4][G][D];
+    __shared__ float cl_o[MAXS][G][D];                 // leader only: landing zone of the splits' partial outputs
+    __shared__ float cl_ml[MAXS][G][2];
+
+    trace_event(p.trace, TR_ATTN | TR_BEGIN);
+    pdl_wait();
+    trace_event(p.trace, TR_ATTN | TR_WAITED);
+    const int len = p.kv_len[qi];                      // keys visible to this query, the new token included
+    const int n_old = len - 1;                         // ... of which this many are already in the cache
+    const int eff = min((int)gridDim.x, max(1, (len + 63) / 64));
+    if (eff == 1 && split > 0) return;                 // uniform over the cluster: nobody waits on a barrier in that case
+    const bool active = split < eff;
+    const int per = (len + eff - 1) / eff;
+    const int begin = split * per, end = min(len, begin + per);
+    const int end_c = min(end, n_old);                 // cached part of this CTA's key range
+    const bool owns_new = active && end == len;
+    const int* bt = p.block_table + (size_t)(p.bt_row ? p.bt_row[qi] : qi) * p.max_pages;
+    const float* row = qkv + (size_t)qi * H * D;
+
+    if (active) {
+        // the first K/V rows are requested before the Q / rotation work so that both latencies overlap
+        uint4 kr[NV], vr[NV], kn[NV], vn[NV];
+        auto fetch = [&](int tok0, uint4 (&kd)[NV], uint4 (&vd)[NV]) {
+            const int tok = min(tok0 + grp, end_c - 1);
+            const int page = bt[tok / p.page_size], off = tok % p.page_size;
+            const size_t base = (((size_t)page * p.Hkv + kvh) * p.page_size + off) * D + sub * DL;
+#pragma unroll
+            for (int i = 0; i < NV; ++i) {
+                kd[i] = ldg_nc_v4(p.kc + base + i * 8);
+                vd[i] = ldg_nc_v4(p.vc + base + i * 8);
+            }
+        };
+        const int t_first = begin + warp * 4;
+        if (t_first < end_c) fetch(t_first, kr, vr);
+
+        // rotation terms of the DL dims this lane owns (shared by the G query heads and the new key): the per-step table
+        // [nq][D/2] of (cos, sin) written by advance_rope_kernel once for all layers, or computed here
+        float cs[DL], sn[DL];
+        if (rope_cs != nullptr) {
+            const float2* tab = rope_cs + (size_t)qi * (D / 2);
+            if (neox) {
+#pragma unroll
+                for (int i = 0; i < DL; i += 2) {
+                    const float4 v = *reinterpret_cast<const float4*>(tab + (sub & 3) * DL + i);
+                    cs[i] = v.x; sn[i] = v.y; cs[i + 1] = v.z; sn[i + 1] = v.w;
+                }
+            } else {
+#pragma unroll
+                for (int i = 0; i < DL; i += 4) {
+                    const float4 v = *reinterpret_cast<const float4*>(tab + sub * (DL / 2) + i / 2);
+                    cs[i] = cs[i + 1] = v.x; sn[i] = sn[i + 1] = v.y;
+                    cs[i + 2] = cs[i + 3] = v.z; sn[i + 2] = sn[i + 3] = v.w;
+                }
+            }
+        } else {
+            const float pos = (float)n_old;
+#pragma unroll
+            for (int i = 0; i < DL; ++i) {
+                const int d = sub * DL + i;
+                const int fi = neox ? (d % (D / 2)) : (d >> 1);
+                sincosf(pos * inv_freq[fi], &sn[i], &cs[i]);
+            }
+        }
+        auto rotate = [&](float (&x)[DL]) {
+            if (neox) {
+#pragma unroll
+                for (int i = 0; i < DL; ++i) {
+                    const float other = __shfl_xor_sync(0xffffffffu, x[i], 4);     // dim d +- D/2 lives in lane sub ^ 4
+                    x[i] = sub < 4 ? x[i] * cs[i] - other * sn[i] : x[i] * cs[i] + other * sn[i];
+                }
+            } else {
+#pragma unroll
+                for (int i = 0; i < DL; i += 2) {
+                    const float a = x[i], b = x[i + 1];
+                    x[i] = a * cs[i] - b * sn[i];
+                    x[i + 1] = a * sn[i] + b * cs[i];
+                }
+            }
+        };
+        auto load_row = [&](const float* src, float (&x)[DL]) {
+#pragma unroll
+            for (int i = 0; i < DL; i += 4) {
+                const float4 v = *reinterpret_cast<const float4*>(src + sub * DL + i);
+                x[i] = v.x; x[i + 1] = v.y; x[i + 2] = v.z; x[i + 3] = v.w;
+            }
+        };
+        float q[G][DL];
+#pragma unroll
+        for (int g = 0; g < G; ++g) {
+            load_row(row + (size_t)(hq0 + g) * D, q[g]);
+            rotate(q[g]);
+#pragma unroll
+            for (int i = 0; i < DL; ++i) q[g][i] *= q_scale;
+        }
+        float m[G], l[G], o[G][DL];
+#pragma unroll
+        for (int g = 0; g < G; ++g) {
+            m[g] = -INFINITY;
+            l[g] = 0.f;
+#pragma unroll
+            for (int i = 0; i < DL; ++i) o[g][i] = 0.f;
+        }
+        auto accumulate = [&](const float (&kf)[DL], const float (&vf)[DL], bool valid) {
+#pragma unroll
+            for (int g = 0; g < G; ++g) {
+                float sc = 0.f;
+#pragma unroll
+                for (int i = 0; i < DL; ++i) sc = fmaf(q[g][i], kf[i], sc);
+                sc += __shfl_xor_sync(0xffffffffu, sc, 1);
+                sc += __shfl_xor_sync(0xffffffffu, sc, 2);
+                sc += __shfl_xor_sync(0xffffffffu, sc, 4);
+                if (!valid) continue;
+                const float mn = fmaxf(m[g], sc);
+                const float alpha = __expf(m[g] - mn), pr = __expf(sc - mn);
+                m[g] = mn;
+                l[g] = l[g] * alpha + pr;
+#pragma unroll
+                for (int i = 0; i < DL; ++i) o[g][i] = fmaf(pr, vf[i], o[g][i] * alpha);
+            }
+        };
+
+        for (int tok0 = t_first; tok0 < end_c; tok0 += 16) {
+            const bool valid = tok0 + grp < end_c;
+            const bool more = tok0 + 16 < end_c;
+            if (more) fetch(tok0 + 16, kn, vn);
+            float kf[DL], vf[DL];
+#pragma unroll
+            for (int i = 0; i < NV; ++i) {
+                const uint32_t kw[4] = {kr[i].x, kr[i].y, kr[i].z, kr[i].w}, vw[4] = {vr[i].x, vr[i].y, vr[i].z, vr[i].w};
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                    const float2 a = h2_to_f2(kw[j]), b = h2_to_f2(vw[j]);
+                    kf[i * 8 + 2 * j] = a.x; kf[i * 8 + 2 * j + 1] = a.y;
+                    vf[i * 8 + 2 * j] = b.x; vf[i * 8 + 2 * j + 1] = b.y;
+                }
+            }
+            accumulate(kf, vf, valid);
+            if (more) {
+#pragma unroll
+                for (int i = 0; i < NV; ++i) { kr[i] = kn[i]; vr[i] = vn[i]; }
+            }
+        }
+        if (owns_new && warp == 0) {
+            // the new token: rotate K, round K/V to the cache precision, write the page slot, fold it in (lane group 0)
+            float kf[DL], vf[DL];
+            load_row(row + (size_t)(p.Hq + kvh) * D, kf);
+            load_row(row + (size_t)(p.Hq + p.Hkv + kvh) * D, vf);
+            rotate(kf);
+            uint32_t kh[DL / 2], vh[DL / 2];
+#pragma unroll
+            for (int i = 0; i < DL; i += 2) {
+                const __half2 a = __floats2half2_rn(kf[i], kf[i + 1]), b = __floats2half2_rn(vf[i], vf[i + 1]);
+                kh[i / 2] = *reinterpret_cast<const uint32_t*>(&a);
+                vh[i / 2] = *reinterpret_cast<const uint32_t*>(&b);
+                const float2 af = __half22float2(a), bf = __half22float2(b);
+                kf[i] = af.x; kf[i + 1] = af.y; vf[i] = bf.x; vf[i + 1] = bf.y;
+            }
+            if (grp == 0 && blockIdx.y % groups_per_kv == 0) {
+                const int page = bt[n_old / p.page_size], off = n_old % p.page_size;
+                const size_t base = (((size_t)page * p.Hkv + kvh) * p.page_size + off) * D + sub * DL;
+#pragma unroll
+                for (int i = 0; i < NV; ++i) {
+                    *reinterpret_cast<uint4*>(kc_w + base + i * 8) = make_uint4(kh[4 * i], kh[4 * i + 1], kh[4 * i + 2], kh[4 * i + 3]);
+                    *reinterpret_cast<uint4*>(vc_w + base + i * 8) = make_uint4(vh[4 * i], vh[4 * i + 1], vh[4 * i + 2], vh[4 * i + 3]);
+                }
+            }
+            accumulate(kf, vf, grp == 0);
+        }
+        trace_event(p.trace, TR_ATTN | TR_MAIN_DONE);
+        pdl_launch_dependents();
+        // merge the 4 lane groups of the warp, then the 4 warps of the CTA
+#pragma unroll
+        for (int g = 0; g < G; ++g) {
+#pragma unroll
+            for (int off = 8; off <= 16; off <<= 1) {
+                const float m2 = __shfl_xor_sync(0xffffffffu, m[g], off);
+                const float l2 = __shfl_xor_sync(0xffffffffu, l[g], off);
+                const float mn = fmaxf(m[g], m2);
+                const float a1 = (m[g] == -INFINITY) ? 0.f : __expf(m[g] - mn);
+                const float a2 = (m2 == -INFINITY) ? 0.f : __expf(m2 - mn);
+#pragma unroll
+                for (int i = 0; i < DL; ++i) {
+                    const float o2 = __shfl_xor_sync(0xffffffffu, o[g][i], off);
+                    o[g][i] = o[g][i] * a1 + o2 * a2;
+                }
+                l[g] = l[g] * a1 + l2 * a2;
+                m[g] = mn;
+            }
+            if (grp == 0) {
+#pragma unroll
+                for (int i = 0; i < DL; ++i) sm_o[warp][g][sub * DL + i] = o[g][i];
+                if (sub == 0) { sm_m[warp][g] = m[g]; sm_l[warp][g] = l[g]; }
+            }
+        }
+        __syncthreads();
+        float* dst_o = eff == 1 ? nullptr : cluster.map_shared_rank(&cl_o[0][0][0], 0);
+        float* dst_ml = eff == 1 ? nullptr : cluster.map_shared_rank(&cl_ml[0][0][0], 0);
+        for (int idx = threadIdx.x; idx < G * D; idx += blockDim.x) {
+            const int g = idx / D, d = idx % D;
+            float mn = -INFINITY;
+#pragma unroll
+            for (int w = 0; w < 4; ++w) mn = fmaxf(mn, sm_m[w][g]);
+            float acc = 0.f, ls = 0.f;
+#pragma unroll
+            for (int w = 0; w < 4; ++w) {
+                const float a = (sm_m[w][g] == -INFINITY) ? 0.f : __expf(sm_m[w][g] - mn);
+                acc += sm_o[w][g][d] * a;
+                ls += sm_l[w][g] * a;
+            }
+            if (eff == 1) {
+                p.out[((size_t)qi * p.Hq + hq0 + g) * D + d] = __float2half_rn(ls > 0.f ? acc / ls : 0.f);
+            } else {
+                dst_o[((size_t)split * G + g) * D + d] = acc;
+                if (d == 0) { dst_ml[(split * G + g) * 2] = mn; dst_ml[(split * G + g) * 2 + 1] = ls; }
+            }
+        }
+    } else {
+        pdl_launch_dependents();
+    }
+    if (eff == 1) { trace_event(p.trace, TR_ATTN | TR_END); return; }
+    cluster.sync();                                    // release/acquire at cluster scope: the partials are visible in rank 0
+    if (split != 0) return;
+    for (int idx = threadIdx.x; idx < G * D; idx += blockDim.x) {
+        const int g = idx / D, d = idx % D;
+        float mn = -INFINITY;
+        for (int sp = 0; sp < eff; ++sp) mn = fmaxf(mn, cl_ml[sp][g][0]);
+        float acc = 0.f, ls = 0.f;
+        for (int sp = 0; sp < eff; ++sp) {
+            const float ms = cl_ml[sp][g][0];
+            const float a = (ms == -INFINITY) ? 0.f : __expf(ms - mn);
+            acc += cl_o[sp][g][d] * a;
+            ls += cl_ml[sp][g][1] * a;
+        }
+        p.out[((size_t)qi * p.Hq + hq0 + g) * D + d] = __float2half_rn(ls > 0.f ? acc / ls : 0.f);
+    }
+    trace_event(p.trace, TR_ATTN | TR_END);
+}
+
+template <int D, int G>
+static int launch_attn_rope_g(const AttnParams& p, const float* qkv, const float* inv_freq, const float2* rope_cs, __half* kc_w,
+                              __half* vc_w, int neox, float q_scale, cudaStream_t s) {
+    auto kern = attn_decode_rope_kernel<D, G>;
+    static bool opted_in = false;          // cluster sizes above 8 are "non-portable": opt in once per kernel instance
+    if (p.n_splits > 8 && !opted_in) {
+        DLP_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeNonPortableClusterSizeAllowed, 1));
+        opted_in = true;
+    }
+    const int gqa = p.Hq / p.Hkv;
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(p.n_splits, p.Hkv * (gqa / G), p.nq);
+    cfg.blockDim = dim3(128);
+    cfg.dynamicSmemBytes = 0;
+    cfg.stream = s;
+    cudaLaunchAttribute attr[2];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = pdl_enabled() ? 1 : 0;
+    attr[1].id = cudaLaunchAttributeClusterDimension;
+    attr[1].val.clusterDim.x = p.n_splits;
+    attr[1].val.clusterDim.y = 1;
+    attr[1].val.clusterDim.z = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 2;
+    DLP_CHECK_CUDA(cudaLaunchKernelEx(&cfg, kern, p, qkv, inv_freq, rope_cs, kc_w, vc_w, neox, q_scale));
+    return 0;
+}
+
+template <int D>
+static int launch_attn_rope(const AttnParams& p, const float* qkv, const float* inv_freq, const float2* rope_cs, __half* kc_w,
+                            __half* vc_w, int neox, float q_scale, cudaStream_t s) {
+    const int gqa = p.Hq / p.Hkv;
+    if (gqa % 4 == 0) return launch_attn_rope_g<D, 4>(p, qkv, inv_freq, rope_cs, kc_w, vc_w, neox, q_scale, s);
+    if (gqa % 2 == 0) return launch_attn_rope_g<D, 2>(p, qkv, inv_freq, rope_cs, kc_w, vc_w, neox, q_scale, s);
+    return launch_attn_rope_g<D, 1>(p, qkv, inv_freq, rope_cs, kc_w, vc_w, neox, q_scale, s);
+}
+
+int attn_decode_rope(const AttnParams& p_in, const float* qkv, const float* inv_freq, const float2* rope_cs, __half* kc_w,
+                     __half* vc_w, int D, int neox, float q_scale, cudaStream_t s) {
+    AttnParams p = p_in;
+    p.trace = trace_buffer();
+    DLP_REQUIRE(inv_freq != nullptr || rope_cs != nullptr, "attn_decode_rope: need inv_freq or a (cos, sin) table");
+    DLP_REQUIRE(p.nq > 0 && p.Hq % p.Hkv == 0, "attn_decode_rope: bad head configuration Hq=%d Hkv=%d", p.Hq, p.Hkv);
+    DLP_REQUIRE(p.n_splits >= 1 && p.n_splits <= 16, "attn_decode_rope: cluster size %d outside 1..16", p.n_splits);
+    if (D == 64) return launch_attn_rope<64>(p, qkv, inv_freq, rope_cs, kc_w, vc_w, neox, q_scale, s);
+    if (D == 128) return launch_attn_rope<128>(p, qkv, inv_freq, rope_cs, kc_w, vc_w, neox, q_scale, s);
+    DLP_REQUIRE(false, "attn_decode_rope: head dim %d unsupported (64, 128)", D);
 }
 
 template <int D>
@@ -225,7 +565,9 @@ static int launch_attn(const AttnParams& p, cudaStream_t s) {
     return 0;
 }
 
-int attn_paged(const AttnParams& p, int D, cudaStream_t s) {
+int attn_paged(const AttnParams& p_in, int D, cudaStream_t s) {
+    AttnParams p = p_in;
+    p.trace = trace_buffer();
     DLP_REQUIRE(p.nq > 0 && p.Hq % p.Hkv == 0, "attn: bad head configuration Hq=%d Hkv=%d", p.Hq, p.Hkv);
     DLP_REQUIRE(p.n_splits >= 1 && (p.n_splits == 1 || (p.part_o && p.part_ml)), "attn: split-KV needs a workspace");
     if (D == 64) return launch_attn<64>(p, s);
@@ -246,12 +588,6 @@ int attn_paged(const AttnParams& p, int D, cudaStream_t s) {
 // planned upgrade.
 namespace dlp {
 
-__device__ __forceinline__ void cp_async16(void* smem, const void* gmem, bool pred) {
-    const uint32_t s = smem_u32(smem);
-    const int sz = pred ? 16 : 0;  // src-size 0 => zero fill
-    asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(s), "l"(gmem), "r"(sz) : "memory");
-}
-__device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_all;" ::: "memory"); }
 
 __device__ __forceinline__ void ldmatrix_x4(uint32_t (&r)[4], const void* smem) {
     asm volatile("ldmatrix.sync.aligned.m8n8.x4.shared.b16 {%0,%1,%2,%3}, [%4];"

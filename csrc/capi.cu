@@ -27,6 +27,9 @@ bool pdl_enabled() {
     return g_pdl != 0;
 }
 void set_pdl(bool on) { g_pdl = on ? 1 : 0; }
+static unsigned long long* g_trace = nullptr;
+unsigned long long* trace_buffer() { return g_trace; }
+void set_trace_buffer(unsigned long long* buf) { g_trace = buf; }
 
 int sm_count() {
     static int cached[64] = {0};
@@ -61,6 +64,7 @@ const char* dlp_last_error(void) { return get_error(); }
 int dlp_version(void) { return 100; }
 int dlp_sm_count(void) { return sm_count(); }
 int dlp_set_pdl(int on) { set_pdl(on != 0); return 0; }
+int dlp_set_trace(void* buf) { set_trace_buffer((unsigned long long*)buf); return 0; }
 
 int dlp_gemv(const dlp_weight* w0, const dlp_weight* w1, const void* x, const float* norm_w, float eps, void* y,
              int ldy, int out_mode, int T, void* stream) {
@@ -266,6 +270,28 @@ int dlp_attn_paged_fused(const void* q, const void* k_cache, const void* v_cache
     p.part_o = part_o; p.part_ml = part_ml; p.counters = counters;
     p.nq = nq; p.Hq = Hq; p.Hkv = Hkv; p.max_pages = max_pages; p.page_size = page_size; p.n_splits = n_splits;
     return attn_paged(p, D, (cudaStream_t)stream);
+}
+
+int dlp_advance_rope(int32_t* seq_len, const int32_t* active, int32_t* pos, int32_t* slot, int32_t* kv_len,
+                     const int32_t* block_table, int max_pages, int page_size, int n, const float* inv_freq, int n_pairs,
+                     float* rope_cs, void* stream) {
+    DLP_REQUIRE(seq_len && pos && slot && block_table && inv_freq && rope_cs, "dlp_advance_rope: null argument");
+    return advance_rope(seq_len, active, pos, slot, kv_len, block_table, max_pages, page_size, n, inv_freq, n_pairs,
+                        (float2*)rope_cs, (cudaStream_t)stream);
+}
+
+int dlp_attn_decode_rope(const float* qkv, const float* inv_freq, const float* rope_cs, void* k_cache, void* v_cache, const int32_t* block_table,
+                         const int32_t* bt_row, const int32_t* kv_len, void* out, int nq, int Hq, int Hkv, int D, int max_pages,
+                         int page_size, int n_splits, int neox, float q_scale, void* stream) {
+    DLP_REQUIRE(qkv && (inv_freq || rope_cs) && k_cache && v_cache && block_table && kv_len && out, "dlp_attn_decode_rope: null argument");
+    DLP_REQUIRE(((uintptr_t)rope_cs & 15) == 0 && ((uintptr_t)qkv & 15) == 0, "dlp_attn_decode_rope: qkv / rope_cs must be 16-byte aligned");
+    AttnParams p;
+    p.q = nullptr; p.kc = (const __half*)k_cache; p.vc = (const __half*)v_cache;
+    p.block_table = block_table; p.bt_row = bt_row; p.kv_len = kv_len; p.out = (__half*)out;
+    p.part_o = nullptr; p.part_ml = nullptr; p.counters = nullptr;
+    p.nq = nq; p.Hq = Hq; p.Hkv = Hkv; p.max_pages = max_pages; p.page_size = page_size; p.n_splits = n_splits;
+    return attn_decode_rope(p, qkv, inv_freq, (const float2*)rope_cs, (__half*)k_cache, (__half*)v_cache, D, neox, q_scale,
+                            (cudaStream_t)stream);
 }
 
 int dlp_attn_paged_static(const void* q, const void* k_cache, const void* v_cache, const int32_t* block_table,

@@ -45,6 +45,11 @@ const char* get_error();
     } while (0)
 
 int sm_count();  // cached multiprocessor count of the current device
+// Device-side timeline (debug / profiling aid, off unless dlp_set_trace() installed a buffer): CTA (0,0,0) thread 0 of an
+// instrumented kernel appends (event id << 48 | globaltimer ns) records.  buf[0] = count, buf[1] = capacity, records follow.
+unsigned long long* trace_buffer();
+void set_trace_buffer(unsigned long long* buf);
+enum TraceId : unsigned { TR_BEGIN = 0, TR_WAITED = 1, TR_MAIN_DONE = 2, TR_END = 3, TR_GEMV = 1 << 8, TR_ROPE = 2 << 8, TR_ATTN = 3 << 8 };
 bool pdl_enabled();  // programmatic dependent launch between consecutive kernels (env DLP_PDL=0 disables)
 void set_pdl(bool on);
 
@@ -228,6 +233,22 @@ __device__ __forceinline__ bool elect_one() {
 // barrier/TMEM set-up overlap the tail of the current one.  Without the launch attribute both are no-ops.
 __device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
 __device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+__device__ __forceinline__ void trace_event(unsigned long long* buf, unsigned id) {
+    if (buf == nullptr || threadIdx.x != 0 || (blockIdx.x | blockIdx.y | blockIdx.z) != 0) return;
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    const unsigned long long i = atomicAdd(buf, 1ull);
+    if (i < (buf[1] & 0xFFFFFFFFull)) buf[2 + i] = ((unsigned long long)id << 48) | (t & 0xFFFFFFFFFFFFull);
+}
+// "all CTAs" mode (bit 63 of buf[1]): every CTA's thread 0 records; id = 0xC000 | (blockIdx.x & 0x3FF) << 4 | event
+__device__ __forceinline__ void trace_event_cta(unsigned long long* buf, unsigned ev) {
+    if (buf == nullptr || threadIdx.x != 0 || !(buf[1] >> 63)) return;
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    const unsigned long long i = atomicAdd(buf, 1ull);
+    const unsigned id = 0xC000u | ((blockIdx.x & 0x3FFu) << 4) | (ev & 0xFu);
+    if (i < (buf[1] & 0xFFFFFFFFull)) buf[2 + i] = ((unsigned long long)id << 48) | (t & 0xFFFFFFFFFFFFull);
+}
 __device__ __forceinline__ void prefetch_l2(const void* p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p)); }
 // One instruction pulls up to `bytes` (multiple of 16, 16 B aligned) of global memory into L2: lets a small kernel warm
 // the weights of the mat-vec that follows it while HBM would otherwise idle.

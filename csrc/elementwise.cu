@@ -141,7 +141,7 @@ __global__ void rope_kv_kernel(const InT* __restrict__ qkv, const int* __restric
                                __half* __restrict__ vc, int Hq, int Hkv, int D, int n_rot, int page_size, int neox, float q_scale,
                                const float* __restrict__ bias, const float* __restrict__ qn, const float* __restrict__ kn,
                                float eps, const char* __restrict__ pf0, unsigned pf0_bytes, const char* __restrict__ pf1,
-                               unsigned pf1_bytes) {
+                               unsigned pf1_bytes, unsigned long long* trace) {
     // one (head, pair) per thread: grid = (T, ceil(H * D/2 / 256)) so that even a single decode token spreads over
     // a dozen CTAs and every load is issued at once (a serial per-thread loop here is pure latency)
     const int t = blockIdx.x;
@@ -152,7 +152,9 @@ __global__ void rope_kv_kernel(const InT* __restrict__ qkv, const int* __restric
         prefetch_share_l2(pf0, pf0_bytes, blockIdx.x * gridDim.y + blockIdx.y, gridDim.x * gridDim.y);
         prefetch_share_l2(pf1, pf1_bytes, blockIdx.x * gridDim.y + blockIdx.y, gridDim.x * gridDim.y);
     }
+    trace_event(trace, TR_ROPE | TR_BEGIN);
     pdl_wait();
+    trace_event(trace, TR_ROPE | TR_WAITED);
     pdl_launch_dependents();
     const bool live = idx < H * half_d;
     if (!EX && !live) return;
@@ -223,7 +225,7 @@ int rope_kv(const void* qkv, int qkv_is_f16, const int* pos, const int* slot, co
     const bool ex = bias != nullptr || qn != nullptr;
     if (qn != nullptr) DLP_REQUIRE(256 % (D / 2) == 0 && (D / 2 >= 32 || (D / 2 & (D / 2 - 1)) == 0), "rope_kv: qk-norm needs D/2 | 256 (D=%d)", D);
     const dim3 grid(T, ((Hq + 2 * Hkv) * (D / 2) + 255) / 256);
-#define DLP_ROPE_LAUNCH(TY, EXF) DLP_CHECK_CUDA(launch_pdl(rope_kv_kernel<TY, EXF>, grid, dim3(256), 0, s, (const TY*)qkv, pos, slot, inv_freq, q_out, kc, vc, Hq, Hkv, D, n_rot, page_size, neox, q_scale, bias, qn, kn, eps, (const char*)pf0, (unsigned)pf0_bytes, (const char*)pf1, (unsigned)pf1_bytes))
+#define DLP_ROPE_LAUNCH(TY, EXF) DLP_CHECK_CUDA(launch_pdl(rope_kv_kernel<TY, EXF>, grid, dim3(256), 0, s, (const TY*)qkv, pos, slot, inv_freq, q_out, kc, vc, Hq, Hkv, D, n_rot, page_size, neox, q_scale, bias, qn, kn, eps, (const char*)pf0, (unsigned)pf0_bytes, (const char*)pf1, (unsigned)pf1_bytes, trace_buffer()))
     if (qkv_is_f16) { if (ex) DLP_ROPE_LAUNCH(__half, true); else DLP_ROPE_LAUNCH(__half, false); }
     else            { if (ex) DLP_ROPE_LAUNCH(float, true);  else DLP_ROPE_LAUNCH(float, false); }
 #undef DLP_ROPE_LAUNCH
@@ -272,6 +274,39 @@ __global__ void advance_kernel(int* __restrict__ seq_len, const int* __restrict_
 int advance(int* seq_len, const int* active, int* pos, int* slot, int* kv_len, const int* block_table, int max_pages,
             int page_size, int n, cudaStream_t s) {
     DLP_CHECK_CUDA(launch_pdl(advance_kernel, dim3((n + 127) / 128), dim3(128), 0, s, seq_len, active, pos, slot, kv_len, block_table, max_pages, page_size, n));
+    return 0;
+}
+
+// Same bookkeeping, one CTA per batch entry, plus the step's RoPE table: rope_cs[s][i] = (cos, sin)(pos[s] * inv_freq[i]).
+// Every layer's attention kernel of this decode step reads the table instead of evaluating sincosf itself.
+__global__ void __launch_bounds__(128) advance_rope_kernel(int* __restrict__ seq_len, const int* __restrict__ active,
+                                                           int* __restrict__ pos, int* __restrict__ slot, int* __restrict__ kv_len,
+                                                           const int* __restrict__ block_table, int max_pages, int page_size,
+                                                           const float* __restrict__ inv_freq, int n_pairs,
+                                                           float2* __restrict__ rope_cs) {
+    const int s = blockIdx.x;
+    pdl_wait();
+    pdl_launch_dependents();
+    const int sid = active ? active[s] : s;
+    const int p = seq_len[sid];
+    __syncthreads();                    // everybody has read the old length before thread 0 bumps it
+    if (threadIdx.x == 0) {
+        pos[s] = p;
+        const int pg = p / page_size;
+        slot[s] = (pg < max_pages) ? block_table[(size_t)sid * max_pages + pg] * page_size + p % page_size : -1;
+        if (kv_len) kv_len[s] = p + 1;
+        seq_len[sid] = p + 1;
+    }
+    for (int i = threadIdx.x; i < n_pairs; i += blockDim.x) {
+        float sn, cs;
+        sincosf((float)p * inv_freq[i], &sn, &cs);
+        rope_cs[(size_t)s * n_pairs + i] = make_float2(cs, sn);
+    }
+}
+int advance_rope(int* seq_len, const int* active, int* pos, int* slot, int* kv_len, const int* block_table, int max_pages,
+                 int page_size, int n, const float* inv_freq, int n_pairs, float2* rope_cs, cudaStream_t s) {
+    DLP_REQUIRE(n > 0 && n_pairs > 0, "advance_rope: bad shape");
+    DLP_CHECK_CUDA(launch_pdl(advance_rope_kernel, dim3(n), dim3(128), 0, s, seq_len, active, pos, slot, kv_len, block_table, max_pages, page_size, inv_freq, n_pairs, rope_cs));
     return 0;
 }
 

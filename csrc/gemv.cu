@@ -310,7 +310,11 @@ __global__ void __launch_bounds__(256, 2) gemv_dense_v3_kernel(const GemvParams 
     if (threadIdx.x == 0) next_unit = 8;
     const bool dyn_rows = p.row_off_dev != nullptr;
     if (!dyn_rows && u < n_units) issue(u, 0); // weights are static: requested before the predecessor has finished
+    trace_event(p.trace, TR_GEMV | TR_BEGIN);
+    trace_event_cta(p.trace, TR_BEGIN);
     pdl_wait();
+    trace_event(p.trace, TR_GEMV | TR_WAITED);
+    trace_event_cta(p.trace, TR_WAITED);
     if (dyn_rows) {
         roff = (*p.row_off_dev) * p.row_off_mul;
         if (u < n_units) issue(u, 0);
@@ -332,6 +336,8 @@ __global__ void __launch_bounds__(256, 2) gemv_dense_v3_kernel(const GemvParams 
         reduce(un, 1);
         u = u2;
     }
+    trace_event(p.trace, TR_GEMV | TR_MAIN_DONE);
+    trace_event_cta(p.trace, TR_MAIN_DONE);
     pdl_launch_dependents();
     __syncthreads();
     // fixed-order combination of the K-chunk partials + fused epilogue
@@ -357,6 +363,8 @@ __global__ void __launch_bounds__(256, 2) gemv_dense_v3_kernel(const GemvParams 
         else reinterpret_cast<__half*>(p.y)[o] = __float2half_rn(gv_silu(v0) * v1);
     }
     if (p.out_mode == GV_PUSH_F32) ar_signal(p.ar_out);
+    trace_event(p.trace, TR_GEMV | TR_END);
+    trace_event_cta(p.trace, TR_END);
 }
 
 template <typename Kern>
@@ -978,7 +986,9 @@ static int launch_gemv(Kern kern, const GemvParams& p, size_t smem, cudaStream_t
     return 0;
 }
 
-int gemv(const GemvParams& p, int wtype, cudaStream_t stream) {
+int gemv(const GemvParams& p_in, int wtype, cudaStream_t stream) {
+    GemvParams p = p_in;
+    p.trace = trace_buffer();
     const int K = p.w0.K, N = p.w0.N, T = p.T;
     DLP_REQUIRE(T == 1 || T == 2 || T == 4, "gemv: T=%d unsupported (1, 2 or 4; use the tcgen05 GEMM above that)", T);
     DLP_REQUIRE(K % 256 == 0, "gemv: K=%d must be a multiple of 256", K);

@@ -39,6 +39,7 @@ struct GemvParams {
     const int* row_off_dev;
     int row_off_mul;
     const float* out_scale_dev;
+    unsigned long long* trace = nullptr;   // device timeline buffer (common.cuh trace_event), normally null
 };
 int moe_route(const float* logits, int T, int n_expert, int top_k, int* ids, float* w, cudaStream_t s);
 
@@ -88,6 +89,7 @@ struct AttnParams {
     float* part_ml;         // [nq, Hq, n_splits, 2]
     int* counters;          // [nq, Hkv * groups] zero-initialised; non-null => the last split CTA combines in-kernel
     int nq, Hq, Hkv, max_pages, page_size, n_splits;
+    unsigned long long* trace = nullptr;   // device timeline buffer, normally null
 };
 
 int gemv(const GemvParams& p, int wtype, cudaStream_t stream);
@@ -111,6 +113,11 @@ int sample(const float* logits, int R, int V, int ld, int top_k, float top_p, fl
 int f32_to_f16(const float* in, __half* out, size_t n, cudaStream_t s);
 int attn_paged(const AttnParams& p, int D, cudaStream_t s);
 int attn_paged_static(AttnParams p, int D, cudaStream_t s);
+// decode step in one launch: RoPE(Q, new K) + paged K/V write + split-KV attention + cluster/DSMEM combine (attention.cu)
+int attn_decode_rope(const AttnParams& p, const float* qkv, const float* inv_freq, const float2* rope_cs, __half* kc_w,
+                     __half* vc_w, int D, int neox, float q_scale, cudaStream_t s);
+int advance_rope(int* seq_len, const int* active, int* pos, int* slot, int* kv_len, const int* block_table, int max_pages,
+                 int page_size, int n, const float* inv_freq, int n_pairs, float2* rope_cs, cudaStream_t s);
 int ar_consume(const float* h_in, float* h_out, const ArIn& a, int K, int T, cudaStream_t s);
 int bump(int* ctr, cudaStream_t s);
 int attn_prefill(const __half* q, const __half* kc, const __half* vc, const int* bt_row, __half* out, int T, int pos0,

@@ -15,6 +15,8 @@ from __future__ import annotations
 import math
 from dataclasses import dataclass, field
 
+import os
+
 import torch
 
 from ..ops import api as ops
@@ -148,6 +150,18 @@ class LlamaEngine:
         self.scratch = None  # fp16 decode buffer for block-quantised weights on the GEMM path (allocated lazily)
         self._graphs: dict[tuple, torch.cuda.CUDAGraph] = {}
         self.sampling = dict(top_k=40, top_p=0.95, min_p=0.05, temp=0.0, seed=0)
+        # decode attention in one launch (RoPE + KV write + split-KV + cluster combine); plain-llama layers with full-width RoPE
+        self.attn_onepass = (dev.type == "cuda" and os.environ.get("DLP_ATTN_ONEPASS", "1") == "1" and cfg.rope_dim == self.D
+                             and not cfg.qkv_bias and not cfg.qk_norm)
+        self.attn_cluster = int(os.environ.get("DLP_ATTN_CLUSTER", "16"))
+        # the cluster launch only pays once the context spans more than one 64-key split; below this many keys the two-kernel
+        # path (RoPE kernel + attention) is used (profiles/r1_attn_onepass_ab.txt).  The host knows every sequence length, so the choice is part of the graph key.
+        self.attn_onepass_min = int(os.environ.get("DLP_ATTN_ONEPASS_MIN", "64"))
+        self._onepass_now = False
+        self._graph_launches: dict[tuple, int] = {}    # kernels inside each captured graph
+        self.launches_replayed = 0                      # kernels launched through graph replays so far
+        self.rope_cs = (torch.zeros(max_seqs, self.D // 2, 2, dtype=f32, device=dev)
+                        if self.attn_onepass and os.environ.get("DLP_ROPE_TABLE", "1") == "1" else None)
         self.eval_callback = None      # fn(name, layer, tensor) called after every layer (eager paths only; disables graphs)
 
     # ---- sequence management ------------------------------------------------------------------
@@ -262,8 +276,11 @@ class LlamaEngine:
             else:
                 ops.linear(lw.wqkv, xn, "f16", out=qkv[:, :lw.wqkv.N], scratch=self._scratch_for(lw.wqkv))
                 ops.linear(lw.wv, xn, "f16", out=qkv[:, lw.wqkv.N:], scratch=self._scratch_for(lw.wv))
-        q = self._rope(il, qkv, T)
-        att = attn_fn(il, q, T)
+        if small and self._onepass_now and attn_fn == self._attn_decode:
+            att = self._attn_decode_onepass(il, qkv, T)
+        else:
+            q = self._rope(il, qkv, T)
+            att = attn_fn(il, q, T)
         if tp:
             d = ops.linear(lw.wo, att, "f32", out=self.delta[:T], scratch=self._scratch_for(lw.wo))
             d = comm.allreduce_delta(d, il, 0)
@@ -302,8 +319,11 @@ class LlamaEngine:
             self.cur ^= 1
         else:
             c.gemv(lw.wqkv, hin, ops.OUT_F32, T, out=self.qkv32[:T], norm_w=lw.attn_norm, eps=cfg.rms_eps)
-        q = self._rope(il, self.qkv32[:T], T)
-        att = attn_fn(il, q, T)
+        if self._onepass_now and attn_fn == self._attn_decode:
+            att = self._attn_decode_onepass(il, self.qkv32[:T], T)
+        else:
+            q = self._rope(il, self.qkv32[:T], T)
+            att = attn_fn(il, q, T)
         c.gemv(lw.wo, att, 4, T, ar_out=c.ar_out(2 * li))
         act = c.gemv(lw.w_gate, self.hb[self.cur], ops.OUT_SWIGLU_F16, T, out=self.act[:T], w_up=lw.w_up, norm_w=lw.ffn_norm,
                      eps=cfg.rms_eps, ar_in=c.ar_in(2 * li, self.hb[1 - self.cur]))
@@ -369,6 +389,12 @@ class LlamaEngine:
         return ops.attn_paged(q, self.kv.k[il], self.kv.v[il], self.kv.block_table, self.kv_len[:T], self.Hq, self.Hkv,
                               self.D, bt_row=self.active[:T], n_splits=self.attn_splits, workspace=self.attn_ws,
                               out=self.att[:T])
+
+    def _attn_decode_onepass(self, il, qkv, T):
+        return ops.attn_decode_rope(qkv, self.inv_freq, self.kv.k[il], self.kv.v[il], self.kv.block_table, self.kv_len[:T],
+                                    self.Hq, self.Hkv, self.D, bt_row=self.active[:T], n_splits=self.attn_cluster,
+                                    neox=self.cfg.rope_neox, attn_scale=self.attn_scale, out=self.att[:T],
+                                    rope_cs=self.rope_cs[:T] if self.rope_cs is not None else None)
 
     def _attn_prefill_for(self, sid: int, pos0: int):
         def fn(il, q, T):
@@ -564,7 +590,8 @@ class LlamaEngine:
     # ---- public: decode -------------------------------------------------------------------------
     def _decode_body(self, B: int, sample: bool):
         """One decode step for the sequence slots listed in self.active[:B]; everything stays on the device."""
-        ops.advance(self.seq_len_dev, self.active, self.pos, self.slot, self.kv_len, self.kv.block_table, self.page_size, B)
+        ops.advance(self.seq_len_dev, self.active, self.pos, self.slot, self.kv_len, self.kv.block_table, self.page_size, B,
+                    inv_freq=self.inv_freq, rope_cs=self.rope_cs)
         fused = self.fused_tp and B in (1, 2, 4)
         sp = self.fused_tp and B > 4
         if sp:   # batched decode in the sequence-parallel layout (embedding happens per token shard inside)
@@ -607,12 +634,20 @@ class LlamaEngine:
         graphable = (use_graph and self.eval_callback is None and self.device.type == "cuda" and not moe_host
                      and not getattr(self.comm, "no_graph", False)
                      and not (self.fused_tp and B > 4))   # SP path passes host-side epochs as kernel arguments
+        self._onepass_now = self.attn_onepass and max(self.seqs[sid].length for sid in sids) + 1 >= self.attn_onepass_min
         if graphable:
-            key = (B, sample) + (tuple(self.sampling.values()) if sample else ())  # sampler scalars are baked into the graph
+            # sampler scalars and the attention variant are baked into the graph
+            key = (B, sample, self._onepass_now) + (tuple(self.sampling.values()) if sample else ())
             g = self._graphs.get(key)
             if g is None:
+                if self.attn_onepass:   # capture the other attention variant now as well: the switch at 64 keys must not stall
+                    want = self._onepass_now
+                    self._onepass_now = not want
+                    self._capture(B, sample, key[:2] + (not want,) + key[3:])
+                    self._onepass_now = want
                 g = self._capture(B, sample, key)
             g.replay()
+            self.launches_replayed += self._graph_launches.get(key, 0)
         else:
             self._decode_body(B, sample)
         for sid in sids:
@@ -640,6 +675,7 @@ class LlamaEngine:
             self._decode_body(B, sample)
         self.launches_per_graph = getattr(self, "launches_per_graph", {})
         self.launches_per_graph[(B, sample)] = ops.launch_count - n0
+        self._graph_launches[key or (B, sample)] = ops.launch_count - n0
         self.seq_len_dev.copy_(saved)
         self.step_ctr.copy_(saved_ctr)
         self._graphs[key or (B, sample)] = g

@@ -264,6 +264,31 @@ def attn_paged(q: torch.Tensor, k_cache: torch.Tensor, v_cache: torch.Tensor, bl
     return out
 
 
+def attn_decode_rope(qkv: torch.Tensor, inv_freq: torch.Tensor, k_cache: torch.Tensor, v_cache: torch.Tensor,
+                     block_table: torch.Tensor, kv_len: torch.Tensor, n_head: int, n_head_kv: int, head_dim: int,
+                     bt_row: torch.Tensor | None = None, n_splits: int = 8, neox: bool = False, attn_scale: float = 1.0,
+                     out: torch.Tensor | None = None, rope_cs: torch.Tensor | None = None) -> torch.Tensor:
+    """One-launch decode attention: RoPE on Q and the new K, K/V page write at position kv_len-1, split-KV attention with the
+    splits combined inside a thread-block cluster.  qkv: fp32 [nq, (Hq+2Hkv)*D] straight from the QKV mat-vec."""
+    nq = qkv.shape[0]
+    if out is None:
+        out = torch.empty(nq, n_head * head_dim, dtype=torch.float16, device=qkv.device)
+    if not native(qkv) or qkv.dtype != torch.float32 or inv_freq.numel() * 2 != head_dim:
+        ps = k_cache.shape[2]
+        pos = (kv_len - 1).to(torch.int32)
+        rows = block_table if bt_row is None else block_table[bt_row.long()]
+        page = rows[torch.arange(nq, device=rows.device), (pos // ps).long()]
+        slot = (page * ps + pos % ps).to(torch.int32)
+        q = rope_kv(qkv, pos, slot, inv_freq, k_cache, v_cache, n_head, n_head_kv, head_dim, neox, attn_scale=attn_scale)
+        return attn_paged(q, k_cache, v_cache, block_table, kv_len, n_head, n_head_kv, head_dim, bt_row=bt_row, out=out)
+    _lib.check(_lib.load().dlp_attn_decode_rope(
+        qkv.data_ptr(), inv_freq.data_ptr(), _p(rope_cs), k_cache.data_ptr(), v_cache.data_ptr(), block_table.data_ptr(), _p(bt_row),
+        kv_len.data_ptr(), out.data_ptr(), nq, n_head, n_head_kv, head_dim, block_table.shape[1], k_cache.shape[2],
+        max(1, min(16, n_splits)), int(neox), attn_scale / math.sqrt(head_dim), _stream()), "attn_decode_rope")
+    _count()
+    return out
+
+
 def attn_prefill(q: torch.Tensor, k_cache: torch.Tensor, v_cache: torch.Tensor, block_table_row: torch.Tensor, pos0: int,
                  n_head: int, n_head_kv: int, head_dim: int, out: torch.Tensor | None = None) -> torch.Tensor:
     """Causal attention of a T-token chunk at positions [pos0, pos0+T) of one sequence."""
@@ -286,8 +311,16 @@ def attn_prefill(q: torch.Tensor, k_cache: torch.Tensor, v_cache: torch.Tensor, 
 
 
 def advance(seq_len: torch.Tensor, active: torch.Tensor | None, pos: torch.Tensor, slot: torch.Tensor,
-            kv_len: torch.Tensor | None, block_table: torch.Tensor, page_size: int, n: int):
-    """Device-side bookkeeping for the n batch entries whose sequence slots are active[:n] (see dlp_advance)."""
+            kv_len: torch.Tensor | None, block_table: torch.Tensor, page_size: int, n: int,
+            inv_freq: torch.Tensor | None = None, rope_cs: torch.Tensor | None = None):
+    """Device-side bookkeeping for the n batch entries whose sequence slots are active[:n] (see dlp_advance).  With
+    `rope_cs` (fp32 [n, D/2, 2]) it also writes the step's (cos, sin) RoPE table for the one-pass attention kernel."""
+    if native(seq_len) and rope_cs is not None:
+        _lib.check(_lib.load().dlp_advance_rope(seq_len.data_ptr(), _p(active), pos.data_ptr(), slot.data_ptr(), _p(kv_len),
+                                                block_table.data_ptr(), block_table.shape[1], page_size, n, inv_freq.data_ptr(),
+                                                inv_freq.numel(), rope_cs.data_ptr(), _stream()), "advance_rope")
+        _count()
+        return
     if not native(seq_len):
         sid = (active[:n] if active is not None else torch.arange(n)).long()
         p = seq_len[sid]

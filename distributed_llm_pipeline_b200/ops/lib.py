@@ -57,6 +57,9 @@ def _declare(lib):
         "dlp_advance": (i32, [vp, vp, vp, vp, vp, vp, i32, i32, i32, vp]),
         "dlp_attn_paged": (i32, [vp, vp, vp, vp, vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, i32, i32, vp]),
         "dlp_attn_paged_fused": (i32, [vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, i32, i32, vp]),
+        "dlp_set_trace": (i32, [vp]),
+        "dlp_advance_rope": (i32, [vp, vp, vp, vp, vp, vp, i32, i32, i32, vp, i32, vp, vp]),
+        "dlp_attn_decode_rope": (i32, [vp, vp, vp, vp, vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, i32, i32, i32, f32, vp]),
         "dlp_attn_prefill": (i32, [vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, i32, vp]),
         "dlp_argmax": (i32, [vp, i32, i32, i32, vp, vp]),
         "dlp_sample": (i32, [vp, i32, i32, i32, i32, f32, f32, f32, u32, vp, vp, vp]),

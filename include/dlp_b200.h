@@ -44,6 +44,11 @@ int dlp_sm_count(void);
 /* Programmatic dependent launch between consecutive kernels of a stream (default on; env DLP_PDL=0 or dlp_set_pdl(0)
  * turns it off for A/B runs).  Kernels call griddepcontrol.wait before reading their predecessor's output. */
 int dlp_set_pdl(int on);
+/* Install (or with NULL remove) a device timeline buffer of uint64: buf[0] = record count (zero it before a run), buf[1] =
+ * capacity, then records (event id << 48 | %globaltimer ns) appended by CTA (0,0,0) of the decode-path kernels
+ * (mat-vec, RoPE, attention: begin / dependency wait returned / main loop done / end).  Kernel launches issued - or graphs
+ * captured - while a buffer is installed carry it; profiling aid only (tools/timeline.py). */
+int dlp_set_trace(void* buf);
 
 /* Decode mat-vec, T in {1,2,4}: y[T,N] (op)= x[T,K] . W^T.  If norm_w != NULL, x is the fp32 residual stream and
  * RMSNorm(x)*norm_w is fused into the prologue; otherwise x is fp16.  out_mode SWIGLU takes w0=gate, w1=up.
@@ -112,6 +117,21 @@ int dlp_attn_paged_fused(const void* q, const void* k_cache, const void* v_cache
                          const int32_t* bt_row, const int32_t* kv_len, void* out, float* part_o, float* part_ml,
                          int32_t* counters, int nq, int Hq, int Hkv, int D, int max_pages, int page_size, int n_splits,
                          void* stream);
+
+/* Whole decode-attention step in one launch (no reference counterpart as a single op: the reference runs ggml_rope_ext,
+ * ggml_set_rows for K and V, flash_attn_ext_vec and flash_attn_combine_results as separate graph nodes,
+ * llama.cpp/src/models/llama.cpp:60-110).  `qkv` is the fp32 [nq, (Hq+2Hkv)*D] output of the QKV mat-vec, not rotated; the
+ * kernel rotates Q and the new token's K (full-width rotation, n_rot == D; `neox` = half-split pairs), writes that token's
+ * K/V at position kv_len-1 of its sequence (page from the block table), attends over kv_len keys and writes `out` fp16
+ * [nq, Hq*D].  The n_splits (1..16) KV splits of a (query, KV-head group) run as one thread-block cluster and combine
+ * through distributed shared memory - no workspace.  kv_len counts the new token.  `rope_cs` (optional) is the step's
+ * [nq][D/2] table of (cos, sin) pairs written by dlp_advance_rope; when NULL the kernel evaluates sincosf from inv_freq. */
+int dlp_advance_rope(int32_t* seq_len, const int32_t* active, int32_t* pos, int32_t* slot, int32_t* kv_len,
+                     const int32_t* block_table, int max_pages, int page_size, int n, const float* inv_freq, int n_pairs,
+                     float* rope_cs, void* stream);
+int dlp_attn_decode_rope(const float* qkv, const float* inv_freq, const float* rope_cs, void* k_cache, void* v_cache, const int32_t* block_table,
+                         const int32_t* bt_row, const int32_t* kv_len, void* out, int nq, int Hq, int Hkv, int D, int max_pages,
+                         int page_size, int n_splits, int neox, float q_scale, void* stream);
 
 /* dlp_attn_paged for callers that cannot supply the split-KV workspace.  (No counterpart in the reference: it always
  * allocates its own split buffers from the backend pool.)

@@ -26,7 +26,7 @@ def test_engine_gpu_matches_oracle(tmp_models, key):
         lg = eng.decode([sid], [t], sample=False)[0]
         assert nmse(ref_logits[i + 1], lg) < 1e-3, i
     if not eng.cfg.is_moe:
-        assert (1, False) in eng._graphs
+        assert any(k[:2] == (1, False) for k in eng._graphs)
 
 
 def test_graph_decode_feeds_back_device_tokens(tmp_models):
@@ -83,3 +83,23 @@ def test_speculative_verify_and_embed_on_gpu(tmp_models):
     ref = ReferenceModel.from_gguf(path)
     h = ref.forward(ids, ref.new_cache(16), return_hidden=True)
     assert nmse(rms_norm(h, ref.w["output_norm.weight"], ref.cfg.rms_eps), e) < 1e-4
+
+
+@pytest.mark.parametrize("key", [("tiny", "F16"), ("tiny128", "F16"), ("tiny", "Q8_0"), ("tiny-phi3", "F16")])
+def test_engine_onepass_attention_matches_oracle(tmp_models, key):
+    """Decode with the one-launch attention step (RoPE + KV write + attention + cluster combine) forced on from the first
+    token (normally it takes over at 64 keys), plus the hand-over between the two variants in the middle of a sequence."""
+    path = tmp_models[key]
+    ref = ReferenceModel.from_gguf(path)
+    toks, ref_logits = ref.generate_greedy(PROMPT, 8)
+    eng = LlamaEngine(load_weights(path, "cuda"), n_ctx=256, max_seqs=4, page_size=16, max_batch_tokens=64)
+    assert eng.attn_onepass
+    eng.attn_onepass_min = 0
+    sid = eng.alloc_seq()
+    eng.prefill(sid, PROMPT)
+    for i, t in enumerate(toks[:-1]):
+        if i == 4:
+            eng.attn_onepass_min = 10 ** 6          # back to the two-kernel path: both read / write the same cache
+        lg = eng.decode([sid], [t], sample=False)[0]
+        assert nmse(ref_logits[i + 1], lg) < 1e-3, i
+    assert any(k[:3] == (1, False, True) for k in eng._graphs) and any(k[:3] == (1, False, False) for k in eng._graphs)

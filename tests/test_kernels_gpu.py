@@ -68,6 +68,33 @@ def test_gemv_fused_norm_and_swiglu(t):
     assert nmse(ref, y) < (2e-4 if t.name.startswith("Q") else 2e-5)
 
 
+@pytest.mark.parametrize("t", [GGMLType.F16, GGMLType.BF16])
+@pytest.mark.parametrize("T", [1, 2, 4])
+@pytest.mark.parametrize("N,K", [(6144, 1024), (4736, 2048), (3072, 3584)])
+def test_gemv_large_shapes(t, T, N, K):
+    """Decode-sized matrices (thousands of rows, the shapes the balanced row ranges / dynamic unit queue are tuned for): every
+    epilogue, repeated launches, bit-identical results run to run."""
+    w, exact = _w(N, K, t, 5)
+    wu, eu = _w(N, K, t, 6)
+    x = (torch.randn(T, K, device=DEV) * 2).half()
+    ref = x.float() @ exact.T
+    for _ in range(3):
+        assert nmse(ref, ops.linear(w, x, "f32")) < 5e-6
+        assert nmse(ref, ops.linear(w, x, "f16")) < 5e-6
+    acc = torch.ones(T, N, device=DEV)
+    ops.linear(w, x, "add", out=acc)
+    ops.linear(w, x, "add", out=acc)
+    assert nmse(2 * ref + 1, acc) < 5e-6
+    h = torch.randn(T, K, device=DEV) * 3
+    nw = torch.rand(K, device=DEV) + 0.5
+    xn = (h * torch.rsqrt(h.pow(2).mean(-1, keepdim=True) + 1e-5) * nw).half().float()
+    refs = torch.nn.functional.silu(xn @ exact.T) * (xn @ eu.T)
+    for _ in range(2):
+        assert nmse(refs, ops.linear(w, h, "swiglu", w_up=wu, norm_w=nw, eps=1e-5)) < 2e-5
+    a, b = ops.linear(w, x, "f32"), ops.linear(w, x, "f32")
+    assert torch.equal(a, b)            # chunk partials are summed in a fixed order: bit-identical run to run
+
+
 @pytest.mark.parametrize("T,N,K", [(5, 128, 64), (16, 256, 256), (37, 384, 1024), (128, 512, 512), (300, 128, 2048), (512, 1024, 4096)])
 @pytest.mark.parametrize("dtype", [torch.float16, torch.bfloat16])
 def test_gemm_tcgen05_store(T, N, K, dtype):
@@ -218,6 +245,40 @@ def test_attn_paged_decode(D, Hq, Hkv, n_splits):
             out2 = ops.attn_paged(q, kc, vc, bt, lens, Hq, Hkv, D, n_splits=n_splits, workspace=ws)
             assert nmse(ref, out2) < 5e-5
         assert int(ws[2].abs().sum()) == 0
+
+
+@pytest.mark.parametrize("D,Hq,Hkv", [(128, 8, 2), (64, 8, 1), (128, 4, 4), (64, 6, 3)])
+@pytest.mark.parametrize("neox", [False, True])
+@pytest.mark.parametrize("n_splits", [1, 8, 16])
+def test_attn_decode_rope_onepass(D, Hq, Hkv, neox, n_splits):
+    """RoPE + K/V page write + split-KV attention + cluster (DSMEM) combine in one launch, against the separate fp32 steps."""
+    page, n_pages, max_pages = 16, 400, 80
+    kc, vc = _fill_cache(n_pages, Hkv, page, D, seed=3)
+    lens = torch.tensor([1, 2, 17, 64, 65, 300, 700, 1200], dtype=torch.int32, device=DEV)   # kv_len includes the new token
+    nq = lens.numel()
+    bt = torch.randperm(n_pages)[: nq * 40].view(nq, 40).to(torch.int32)
+    bt = torch.cat([bt, torch.zeros(nq, max_pages - 40, dtype=torch.int32)], 1).to(DEV)          # 8 x 40 pages of 16 = 640 < 1200?
+    lens = torch.minimum(lens, torch.tensor(40 * page, device=DEV)).to(torch.int32)
+    H = Hq + 2 * Hkv
+    qkv = torch.randn(nq, H * D, device=DEV)
+    inv = (10000.0 ** (-torch.arange(0, D // 2).double() * 2 / D)).float().to(DEV)
+    # oracle: CPU rope + cache write + attention on copies of the cache
+    kc_ref, vc_ref = kc.cpu().clone(), vc.cpu().clone()
+    pos = (lens - 1).cpu()
+    slot = (bt.cpu()[torch.arange(nq), (pos // page).long()] * page + pos % page).to(torch.int32)
+    q_ref = ops.rope_kv(qkv.cpu(), pos.to(torch.int32), slot, inv.cpu(), kc_ref, vc_ref, Hq, Hkv, D, neox)
+    ref = ops._attn_cpu(q_ref, kc_ref, vc_ref, bt.cpu(), lens.cpu(), Hq, Hkv, D)
+    ang = pos.float()[:, None] * inv.cpu()[None]
+    table = torch.stack([ang.cos(), ang.sin()], -1).contiguous().to(DEV)      # the per-step table advance_rope writes
+    for tab in (None, table):      # in-kernel sincos, then the table; the second call rewrites the same slots with the same values
+        out = ops.attn_decode_rope(qkv, inv, kc, vc, bt, lens, Hq, Hkv, D, n_splits=n_splits, neox=neox, rope_cs=tab)
+        assert nmse(ref, out) < 5e-5
+    pg, off = (slot // page).long(), (slot % page).long()
+    assert nmse(kc_ref[pg, :, off], kc.cpu()[pg, :, off]) < 1e-6
+    assert nmse(vc_ref[pg, :, off], vc.cpu()[pg, :, off]) < 1e-6
+    untouched = torch.ones(n_pages, dtype=torch.bool)
+    untouched[pg] = False
+    assert torch.equal(kc.cpu()[untouched], kc_ref[untouched])          # nothing else in the cache was written
 
 
 @pytest.mark.parametrize("D,Hq,Hkv", [(128, 8, 2), (64, 4, 2)])

@@ -18,9 +18,16 @@ ap.add_argument("--prefill", type=int, default=512)
 ap.add_argument("--decode", type=int, default=3)
 ap.add_argument("--layers", type=int, default=0, help="profile only the first N layers (0 = all)")
 a = ap.parse_args()
-path = ensure_model(a.model, a.ftype, 0, lambda: None)
-rng = range(a.layers) if a.layers else None
-w = load_weights(path, "cuda:0", layer_range=rng)
+if a.layers:      # same layer shapes, fewer layers: a 4-layer file is written in seconds instead of a minute
+    from bench import MODEL_DIR
+    from distributed_llm_pipeline_b200.gguf import write_synthetic_gguf
+    from distributed_llm_pipeline_b200.models.config import preset
+    path = os.path.join(MODEL_DIR, f"{a.model}-{a.layers}L-{a.ftype}.gguf")
+    if not os.path.exists(path):
+        write_synthetic_gguf(path, preset(a.model, n_layer=a.layers), a.ftype, seed=0)
+else:
+    path = ensure_model(a.model, a.ftype, 0, lambda: None)
+w = load_weights(path, "cuda:0")
 eng = LlamaEngine(w, n_ctx=2048, max_seqs=1, page_size=64, max_batch_tokens=max(a.prefill, 16))
 sid = eng.alloc_seq()
 g = torch.Generator().manual_seed(0)
