@@ -329,9 +329,16 @@ __global__ void __launch_bounds__(128) attn_decode_rope_kernel(const AttnParams 
             }
         };
         float q[G][DL];
+        float kf_new[DL], vf_new[DL];
+        const bool do_new = owns_new && warp == 0;     // the new token's K/V rows travel with the Q rows: one L2 round trip
+        if (do_new) {
+            load_row(row + (size_t)(p.Hq + kvh) * D, kf_new);
+            load_row(row + (size_t)(p.Hq + p.Hkv + kvh) * D, vf_new);
+        }
+#pragma unroll
+        for (int g = 0; g < G; ++g) load_row(row + (size_t)(hq0 + g) * D, q[g]);
 #pragma unroll
         for (int g = 0; g < G; ++g) {
-            load_row(row + (size_t)(hq0 + g) * D, q[g]);
             rotate(q[g]);
 #pragma unroll
             for (int i = 0; i < DL; ++i) q[g][i] *= q_scale;
@@ -363,6 +370,30 @@ __global__ void __launch_bounds__(128) attn_decode_rope_kernel(const AttnParams 
             }
         };
 
+        if (do_new) {
+            // the new token first (online softmax does not care about order): rotate K, round K/V to the cache precision,
+            // write the page slot, fold it in (lane group 0)
+            rotate(kf_new);
+            uint32_t kh[DL / 2], vh[DL / 2];
+#pragma unroll
+            for (int i = 0; i < DL; i += 2) {
+                const __half2 a = __floats2half2_rn(kf_new[i], kf_new[i + 1]), b = __floats2half2_rn(vf_new[i], vf_new[i + 1]);
+                kh[i / 2] = *reinterpret_cast<const uint32_t*>(&a);
+                vh[i / 2] = *reinterpret_cast<const uint32_t*>(&b);
+                const float2 af = __half22float2(a), bf = __half22float2(b);
+                kf_new[i] = af.x; kf_new[i + 1] = af.y; vf_new[i] = bf.x; vf_new[i + 1] = bf.y;
+            }
+            if (grp == 0 && blockIdx.y % groups_per_kv == 0) {
+                const int page = bt[n_old / p.page_size], off = n_old % p.page_size;
+                const size_t base = (((size_t)page * p.Hkv + kvh) * p.page_size + off) * D + sub * DL;
+#pragma unroll
+                for (int i = 0; i < NV; ++i) {
+                    *reinterpret_cast<uint4*>(kc_w + base + i * 8) = make_uint4(kh[4 * i], kh[4 * i + 1], kh[4 * i + 2], kh[4 * i + 3]);
+                    *reinterpret_cast<uint4*>(vc_w + base + i * 8) = make_uint4(vh[4 * i], vh[4 * i + 1], vh[4 * i + 2], vh[4 * i + 3]);
+                }
+            }
+            accumulate(kf_new, vf_new, grp == 0);
+        }
         for (int tok0 = t_first; tok0 < end_c; tok0 += 16) {
             const bool valid = tok0 + grp < end_c;
             const bool more = tok0 + 16 < end_c;
@@ -383,32 +414,6 @@ __global__ void __launch_bounds__(128) attn_decode_rope_kernel(const AttnParams 
 #pragma unroll
                 for (int i = 0; i < NV; ++i) { kr[i] = kn[i]; vr[i] = vn[i]; }
             }
-        }
-        if (owns_new && warp == 0) {
-            // the new token: rotate K, round K/V to the cache precision, write the page slot, fold it in (lane group 0)
-            float kf[DL], vf[DL];
-            load_row(row + (size_t)(p.Hq + kvh) * D, kf);
-            load_row(row + (size_t)(p.Hq + p.Hkv + kvh) * D, vf);
-            rotate(kf);
-            uint32_t kh[DL / 2], vh[DL / 2];
-#pragma unroll
-            for (int i = 0; i < DL; i += 2) {
-                const __half2 a = __floats2half2_rn(kf[i], kf[i + 1]), b = __floats2half2_rn(vf[i], vf[i + 1]);
-                kh[i / 2] = *reinterpret_cast<const uint32_t*>(&a);
-                vh[i / 2] = *reinterpret_cast<const uint32_t*>(&b);
-                const float2 af = __half22float2(a), bf = __half22float2(b);
-                kf[i] = af.x; kf[i + 1] = af.y; vf[i] = bf.x; vf[i + 1] = bf.y;
-            }
-            if (grp == 0 && blockIdx.y % groups_per_kv == 0) {
-                const int page = bt[n_old / p.page_size], off = n_old % p.page_size;
-                const size_t base = (((size_t)page * p.Hkv + kvh) * p.page_size + off) * D + sub * DL;
-#pragma unroll
-                for (int i = 0; i < NV; ++i) {
-                    *reinterpret_cast<uint4*>(kc_w + base + i * 8) = make_uint4(kh[4 * i], kh[4 * i + 1], kh[4 * i + 2], kh[4 * i + 3]);
-                    *reinterpret_cast<uint4*>(vc_w + base + i * 8) = make_uint4(vh[4 * i], vh[4 * i + 1], vh[4 * i + 2], vh[4 * i + 3]);
-                }
-            }
-            accumulate(kf, vf, grp == 0);
         }
         trace_event(p.trace, TR_ATTN | TR_MAIN_DONE);
         pdl_launch_dependents();
