@@ -20,16 +20,22 @@ HOT = [
     ("gemm_tcgen05_bt256_q8_0_fused_dequant", r"gemm_tcgen05_kernel<256, 1, 0, 8>"),
     ("gemm_tcgen05_bt256_q4_k_fused_dequant", r"gemm_tcgen05_kernel<256, 1, 0, 12>"),
     ("gemm_tcgen05_bt16_dense", r"gemm_tcgen05_kernel<16, 1, 0, 1>"),
+    ("gemv_dense_v3_f16_t1", r"gemv_dense_v3_kernel<1, false, 4, 2>"),
+    ("gemv_quant_v3_q8_0_t1", r"gemv_quant_v3_kernel<8, 1>"),
+    ("gemv_quant_v3_q4_k_t1", r"gemv_quant_v3_kernel<12, 1>"),
+    ("attn_decode_rope_d128_g4_cluster", r"attn_decode_rope_kernel<128, 4>"),
+    ("advance_rope", r"advance_rope_kernel"),
     ("gemv_dense_f16_t1", r"gemv_dense_kernel<1, false>"),
     ("gemv_quant_q8_0_t1", r"gemv_quant_kernel<8, 1>"),
     ("gemv_quant_q4_k_t1", r"gemv_quant_kernel<12, 1>"),
     ("attn_decode_d128_g4", r"attn_decode_kernel<128, 4>"),
     ("attn_prefill_d128", r"attn_prefill_kernel<128>"),
-    ("rope_kv_f32", r"rope_kv_kernel<float>"),
+    ("rope_kv_f32", r"rope_kv_kernel<float, false>"),
+    ("rope_kv_f32_bias_qknorm", r"rope_kv_kernel<float, true>"),
     ("rmsnorm", r"rmsnorm_kernel"),
     ("sample", r"sample_kernel"),
 ]
-KEY = ["UTCHMMA", "UTCQMMA", "LDTM", "STTM", "UTMALDG", "UTMASTG", "UTCBAR", "SYNCS", "HMMA", "LDGSTS", "LDSM", "FFMA", "HFMA2", "LDG", "STG", "RED", "ATOM"]
+KEY = ["UCGABAR_ARV", "UCGABAR_WAIT", "MAPA", "MEMBAR", "ACQBULK", "UBLKPF", "UTCHMMA", "UTCQMMA", "LDTM", "STTM", "UTMALDG", "UTMASTG", "UTCBAR", "SYNCS", "HMMA", "LDGSTS", "LDSM", "FFMA", "HFMA2", "LDG", "STG", "RED", "ATOM"]
 
 
 def main():
