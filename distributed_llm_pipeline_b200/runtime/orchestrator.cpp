@@ -206,7 +206,7 @@ std::string sse_event(const std::string& type, const std::string& content) {
 
 // ---- HTTP request parsing ----------------------------------------------------------------------------------------
 struct HttpRequest {
-    std::string method, path;
+    std::string method, path, target;
     std::map<std::string, std::string> headers;
     std::string body;
 };
@@ -227,6 +227,7 @@ bool read_request(int fd, HttpRequest& rq) {
     if (!std::getline(hs, line)) return false;
     std::istringstream rl(line);
     rl >> rq.method >> target >> version;
+    rq.target = target;
     rq.path = target.substr(0, target.find('?'));
     while (std::getline(hs, line)) {
         if (!line.empty() && line.back() == '\r') line.pop_back();
@@ -376,6 +377,34 @@ void proxy_get(int fd, const std::string& path) {  // /health, /metrics, /slots 
     send_simple(fd, "200 OK", path == "/metrics" ? "text/plain; version=0.0.4" : "application/json", c);
 }
 
+// Every API route the front-end does not serve itself (/completion, /v1/*, /embedding, /tokenize, /slots/.., /props, ...) is
+// tunnelled to the engine service: request line + headers as one JSON line, the body as raw bytes, and the service's complete
+// HTTP response (chunked SSE streams included) relayed verbatim.  Closing either side cancels the request.
+void proxy_http(int fd, const HttpRequest& rq) {
+    int be = connect_to(g_cfg.backend_host, g_cfg.backend_port);
+    if (be < 0) { send_simple(fd, "503 Service Unavailable", "application/json", "{\"error\":\"engine service is loading\"}"); return; }
+    std::string hdr = "{\"op\":\"http\",\"method\":\"" + json_escape(rq.method) + "\",\"target\":\"" + json_escape(rq.target) + "\",\"headers\":{";
+    bool first = true;
+    for (const auto& kv : rq.headers) {
+        if (kv.first != "authorization" && kv.first != "x-api-key" && kv.first != "content-type" && kv.first != "accept") continue;
+        hdr += std::string(first ? "" : ",") + "\"" + json_escape(kv.first) + "\":\"" + json_escape(kv.second) + "\"";
+        first = false;
+    }
+    hdr += "},\"body_len\":" + std::to_string(rq.body.size()) + "}\n";
+    if (!send_all(be, hdr) || !send_all(be, rq.body)) { ::close(be); send_simple(fd, "502 Bad Gateway", "application/json", "{\"error\":\"engine service closed the connection\"}"); return; }
+    char tmp[16384];
+    for (;;) {
+        pollfd p{be, POLLIN, 0};
+        int r = poll(&p, 1, 1000);
+        if (r == 0) { if (client_gone(fd)) break; continue; }
+        if (r < 0) { if (errno == EINTR) continue; break; }
+        ssize_t n = ::recv(be, tmp, sizeof tmp, 0);
+        if (n <= 0) break;
+        if (!send_all(fd, tmp, (size_t)n)) break;
+    }
+    ::close(be);
+}
+
 void handle_connection(int fd) {
     int one = 1;
     setsockopt(fd, IPPROTO_TCP, TCP_NODELAY, &one, sizeof one);
@@ -389,6 +418,8 @@ void handle_connection(int fd) {
             handle_chat(fd, rq);
         } else if (rq.method == "GET" && (rq.path == "/health" || rq.path == "/metrics" || rq.path == "/slots")) {
             proxy_get(fd, rq.path);
+        } else if (rq.method == "POST" || (rq.method == "GET" && (rq.path == "/props" || rq.path == "/v1/models"))) {
+            proxy_http(fd, rq);
         } else if (rq.method == "GET" || rq.method == "HEAD") {
             serve_static(fd, rq);
         } else {

@@ -46,6 +46,12 @@ class _Handler(socketserver.StreamRequestHandler):
                 body = json.dumps({"status": "ok"})
             self._send({"c": body})
             return
+        if msg.get("op") == "http":
+            # raw tunnel for every route the native front-end does not implement itself: the request line / headers arrive as
+            # JSON, the body as `body_len` raw bytes; the full HTTP response (SSE streams included) is written back verbatim
+            body = self.rfile.read(int(msg.get("body_len", 0))) if int(msg.get("body_len", 0)) > 0 else b""
+            self._tunnel(msg, body)
+            return
         if msg.get("op") != "generate":
             self._send({"t": "error", "c": "unknown op"})
             return
@@ -90,14 +96,44 @@ class _Handler(socketserver.StreamRequestHandler):
         self.wfile.write(json.dumps(obj, ensure_ascii=False).encode() + b"\n")
         self.wfile.flush()
 
+    def _tunnel(self, msg, body: bytes):
+        import asyncio
+        wfile = self.wfile
+
+        class _Writer:                       # the two StreamWriter methods Orchestrator uses
+            def write(self, data: bytes):
+                wfile.write(data)
+
+            async def drain(self):
+                wfile.flush()
+
+            def close(self):
+                pass
+
+        orch = self.server.orch
+        target = str(msg.get("target", "/"))
+        path, _, query = target.partition("?")
+        headers = {str(k).lower(): str(v) for k, v in (msg.get("headers") or {}).items()}
+
+        async def run():
+            orch._query = dict(kv.partition("=")[::2] for kv in query.split("&") if kv)
+            await orch.route(str(msg.get("method", "GET")).upper(), path, headers, body, None, _Writer())
+
+        try:
+            asyncio.run(run())
+            wfile.flush()
+        except (OSError, ValueError):
+            pass
+
 
 class EngineService(socketserver.ThreadingTCPServer):
     allow_reuse_address = True
     daemon_threads = True
 
-    def __init__(self, addr, sched, startup_logs):
+    def __init__(self, addr, sched, startup_logs, orch=None):
         super().__init__(addr, _Handler)
         self.sched, self.startup_logs = sched, startup_logs
+        self.orch = orch                     # serving.orchestrator.Orchestrator: route table for the raw HTTP tunnel
 
 
 def main(argv=None):
@@ -109,13 +145,23 @@ def main(argv=None):
     ap.add_argument("-np", "--parallel", type=int, default=4)
     ap.add_argument("-b", "--batch-size", type=int, default=2048)
     ap.add_argument("--device", default="cuda")
+    ap.add_argument("-n", "--predict", type=int, default=200)
+    ap.add_argument("--lora", default=None)
+    ap.add_argument("--api-key", default=None)
+    ap.add_argument("--max-queue", type=int, default=0)
+    ap.add_argument("--slot-save-path", default=None)
+    ap.add_argument("--context-shift", action="store_true")
     a = ap.parse_args(argv)
     sched, info, logs = build_service(a.model, a.device, a.ctx_size, a.parallel, a.batch_size, lora=lora_from_args(a))
     for l in logs:
         sys.stderr.write(l)
     sys.stderr.flush()
+    sched.context_shift = a.context_shift
     sched.start()
-    srv = EngineService((a.host, a.port), sched, logs)
+    from .orchestrator import Orchestrator
+    orch = Orchestrator(sched, info, n_predict=a.predict, startup_logs=logs, api_key=a.api_key, max_queue=a.max_queue,
+                        slot_save_path=a.slot_save_path)
+    srv = EngineService((a.host, a.port), sched, logs, orch)
     sys.stderr.write(f"engine service listening on {a.host}:{srv.server_address[1]}\n")
     sys.stderr.flush()
     try:

@@ -92,6 +92,44 @@ def test_native_rejects_bad_json_and_serves_static(front):
     assert b"200 OK" in data and b"/chat" in data and b"text/html" in data
 
 
+def _http(port, method, target, body=b""):
+    s = socket.create_connection(("127.0.0.1", port), timeout=120)
+    s.sendall(f"{method} {target} HTTP/1.1\r\nHost: x\r\nContent-Type: application/json\r\nContent-Length: {len(body)}\r\n\r\n".encode() + body)
+    data = b""
+    while True:
+        c = s.recv(65536)
+        if not c:
+            break
+        data += c
+    s.close()
+    head, _, payload = data.partition(b"\r\n\r\n")
+    return head.decode(), payload
+
+
+def test_native_front_end_tunnels_the_api_routes(front):
+    """Routes the C++ front-end does not implement itself reach the engine service through the raw HTTP tunnel."""
+    fport, _ = front
+    _post_chat(fport, json.dumps({"prompt": "warm"}).encode())      # make sure the engine service is up
+    head, body = _http(fport, "POST", "/completion", json.dumps({"prompt": "a b c", "n_predict": 4, "temperature": 0}).encode())
+    assert " 200 " in head and json.loads(body)["tokens_predicted"] <= 4
+    head, body = _http(fport, "POST", "/v1/chat/completions",
+                       json.dumps({"messages": [{"role": "user", "content": "hi"}], "max_tokens": 3, "temperature": 0}).encode())
+    assert json.loads(body)["object"] == "chat.completion"
+    head, body = _http(fport, "POST", "/tokenize", json.dumps({"content": "hello world"}).encode())
+    toks = json.loads(body)["tokens"]
+    head, body = _http(fport, "POST", "/detokenize", json.dumps({"tokens": toks}).encode())
+    assert json.loads(body)["content"].strip() == "hello world"
+    head, body = _http(fport, "POST", "/embedding", json.dumps({"content": "hello"}).encode())
+    assert len(json.loads(body)["embedding"]) == 256
+    head, body = _http(fport, "GET", "/props")
+    assert json.loads(body)["total_slots"] == 2
+    head, body = _http(fport, "POST", "/slots/0?action=erase", b"{}")
+    assert " 200 " in head and "n_erased" in json.loads(body)
+    # streamed completion: the service's chunked SSE response is relayed verbatim
+    head, body = _http(fport, "POST", "/completion", json.dumps({"prompt": "x y", "n_predict": 3, "temperature": 0, "stream": True}).encode())
+    assert "text/event-stream" in head.lower() and b"data: " in body
+
+
 def test_native_supervisor_restarts_engine_service(front):
     fport, bport = front
     # kill the engine service; the front-end must bring it back and serve the next request
