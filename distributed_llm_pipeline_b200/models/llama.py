@@ -162,6 +162,7 @@ class LlamaEngine:
         self.launches_replayed = 0                      # kernels launched through graph replays so far
         self.rope_cs = (torch.zeros(max_seqs, self.D // 2, 2, dtype=f32, device=dev)
                         if self.attn_onepass and os.environ.get("DLP_ROPE_TABLE", "1") == "1" else None)
+        self.cvec: dict[int, torch.Tensor] = {}     # layer -> fp32 [E] added to the residual stream after that layer
         self.eval_callback = None      # fn(name, layer, tensor) called after every layer (eager paths only; disables graphs)
 
     # ---- sequence management ------------------------------------------------------------------
@@ -408,6 +409,8 @@ class LlamaEngine:
 
     def _run_layers(self, T: int, attn_fn, fused: bool = False):
         if fused:
+            if self.cvec:
+                raise NotImplementedError("control vectors are not supported on the fused tensor-parallel decode path")
             self.cur, self.pending = 0, None
             self.comm.begin_step()
             for il in self.w.layer_range:
@@ -415,8 +418,31 @@ class LlamaEngine:
             return
         for il in self.w.layer_range:
             self._layer(il, T, attn_fn)
+            if il in self.cvec:                     # control vector: h += direction[il] (llama-adapter.cpp apply_to)
+                self.h[:T].add_(self.cvec[il])
             if self.eval_callback is not None:      # tensor inspection hook (ggml-backend.cpp:1584-1616, examples/eval-callback)
                 self.eval_callback("l_out", il, self.h[:T])
+
+    def set_control_vector(self, src, scale: float = 1.0, layer_range: tuple[int, int] | None = None):
+        """Load a control vector (GGUF with `direction.<layer>` tensors [n_embd], as written by the reference's
+        cvector-generator; `llama_adapter_cvec`, `llama.cpp/src/llama-adapter.cpp`) or a {layer: tensor} dict; `None` clears.
+        Cached decode graphs are dropped because the set of launches changes."""
+        self.cvec = {}
+        self._graphs.clear()
+        if src is None:
+            return
+        if isinstance(src, str):
+            from ..gguf import open_gguf
+            import numpy as np
+            f = open_gguf(src)
+            src = {int(n.split(".")[1]): torch.from_numpy(np.array(f.array(n), dtype=np.float32, copy=True))
+                   for n in f.tensors if n.startswith("direction.")}
+        lo, hi = layer_range or (0, self.cfg.n_layer)
+        for il, v in src.items():
+            if lo <= il < hi and il in self.w.layers:
+                if v.numel() != self.E:
+                    raise ValueError(f"control vector for layer {il} has {v.numel()} elements, model has n_embd={self.E}")
+                self.cvec[il] = (v.float() * scale).to(self.device)
 
     def memory_breakdown(self) -> dict:
         """Bytes held on this rank's device by category (`llama_memory_breakdown_print`, llama.h:1501)."""

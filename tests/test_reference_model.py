@@ -1,4 +1,5 @@
 """CPU engine path (torch fallbacks over the paged-KV data layout) against the fp32 oracle."""
+import os
 import pytest
 import torch
 
@@ -165,3 +166,44 @@ def test_yarn_rope_scaling(tmp_path):
     assert nmse(want, got.float().flatten()) < 1e-5
     plain = ReferenceModel.from_gguf(write_synthetic_gguf(str(tmp_path / "plain.gguf"), preset("tiny"), "F16", seed=2))
     assert nmse(plain.forward(prompt, plain.new_cache(64))[-1], want) > 1e-4             # and it is not a no-op
+
+
+def test_export_lora_and_control_vector(tmp_models, tmp_path):
+    import subprocess
+    import sys as _sys
+    import numpy as np
+    from distributed_llm_pipeline_b200.gguf import GGMLType, GGUFWriter
+    from distributed_llm_pipeline_b200.models.weights import LoraAdapter, write_lora_gguf
+    path = tmp_models[("tiny", "F16")]
+    rng = np.random.default_rng(1)
+    ref = ReferenceModel.from_gguf(path)
+    out_f, in_f = ref.w["blk.0.attn_output.weight"].shape
+    apath = write_lora_gguf(str(tmp_path / "a.gguf"), {"blk.0.attn_output.weight": (rng.standard_normal((2, in_f)).astype(np.float32) * 0.1,
+                                                                                      rng.standard_normal((out_f, 2)).astype(np.float32) * 0.1)}, 4.0)
+    merged = str(tmp_path / "merged.gguf")
+    repo = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    r = subprocess.run([_sys.executable, os.path.join(repo, "tools", "dlp_export_lora.py"), "-m", path, "--lora-scaled", apath, "0.5", "-o", merged],
+                       capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    prompt = list(range(5, 15))
+    a = LlamaEngine(load_weights(path, "cpu", lora=[LoraAdapter(apath, 0.5)]), n_ctx=64, max_seqs=1, page_size=16, max_batch_tokens=32)
+    b = LlamaEngine(load_weights(merged, "cpu"), n_ctx=64, max_seqs=1, page_size=16, max_batch_tokens=32)
+    la, lb = a.prefill(a.alloc_seq(), prompt), b.prefill(b.alloc_seq(), prompt)
+    assert nmse(la.float(), lb.float()) < 1e-6
+    # control vector: h += direction[il] after layer il (oracle: same addition in the reference forward)
+    w = GGUFWriter(str(tmp_path / "cvec.gguf"))
+    w.add("general.architecture", "controlvector")
+    d1 = (rng.standard_normal(ref.cfg.n_embd) * 0.5).astype("<f4")
+    w.add_tensor("direction.1", d1.shape, GGMLType.F32, lambda: d1.view(np.uint8).reshape(-1))
+    w.write()
+    eng = LlamaEngine(load_weights(path, "cpu"), n_ctx=64, max_seqs=1, page_size=16, max_batch_tokens=32)
+    eng.set_control_vector(str(tmp_path / "cvec.gguf"), scale=2.0)
+    got = eng.prefill(eng.alloc_seq(), prompt)
+    cache = ref.new_cache(32)
+    h = ref.embed(torch.tensor(prompt))
+    pos = torch.arange(len(prompt))
+    for il in range(ref.cfg.n_layer):
+        h = ref.layer(il, h, pos, cache)
+        if il == 1:
+            h = h + 2.0 * torch.from_numpy(d1)
+    assert nmse(ref.head(h)[-1], got.float().flatten()) < 1e-5

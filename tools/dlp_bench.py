@@ -2,7 +2,7 @@
 """dlp-bench: prompt-processing / text-generation throughput, llama-bench style.
 
 Parity: `llama-bench` (`llama.cpp/tools/llama-bench/llama-bench.cpp:1962-2010`): `-p` prompt sizes, `-n` generation sizes,
-`-r` repetitions, random token ids (valid with random-init weights), outputs md / json / csv with avg_ts +- stddev.
+`-r` repetitions, random token ids (valid with random-init weights), outputs md / json / jsonl / csv / sql with avg_ts +- stddev.
 Device-timed with CUDA events; under torchrun it runs the pp x tp grid and reports the max over ranks.
 """
 import json
@@ -20,7 +20,7 @@ BENCH = [
     Opt(("-p", "--n-prompt"), "comma separated prompt sizes", "512", str),
     Opt(("-n", "--n-gen"), "comma separated generation sizes", "128", str),
     Opt(("-r", "--repetitions"), "repetitions per test", 3, int),
-    Opt(("-o", "--output"), "md | json | csv", "md", str, choices=("md", "json", "csv")),
+    Opt(("-o", "--output"), "md | json | jsonl | csv | sql", "md", str, choices=("md", "json", "jsonl", "csv", "sql")),
     Opt(("--batch",), "decode batch size (sequences decoded together)", 1, int),
 ]
 
@@ -118,6 +118,17 @@ def main(argv=None):
                 "tp_impl": a.tp_impl if grid.tp > 1 else None, "backend": "dlp_b200"}
         if a.output == "json":
             print(json.dumps([dict(meta, **r) for r in rows], indent=1))
+        elif a.output == "jsonl":
+            for r in rows:
+                print(json.dumps(dict(meta, **r)))
+        elif a.output == "sql":      # same idea as llama-bench -o sql: a table definition plus one INSERT per test
+            print("CREATE TABLE IF NOT EXISTS test (model TEXT, params INTEGER, size_bytes INTEGER, pp INTEGER, tp INTEGER, tp_impl TEXT, "
+                  "backend TEXT, test TEXT, n_prompt INTEGER, n_gen INTEGER, avg_ts REAL, stddev_ts REAL);")
+            for r in rows:
+                d = dict(meta, **r)
+                vals = ", ".join("NULL" if d[k] is None else (f"'{d[k]}'" if isinstance(d[k], str) else f"{d[k]}")
+                                 for k in ("model", "params", "size_bytes", "pp", "tp", "tp_impl", "backend", "test", "n_prompt", "n_gen", "avg_ts", "stddev_ts"))
+                print(f"INSERT INTO test VALUES ({vals});")
         elif a.output == "csv":
             print("model,pp,tp,test,avg_ts,stddev_ts")
             for r in rows:
