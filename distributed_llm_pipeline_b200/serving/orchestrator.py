@@ -80,6 +80,7 @@ class Orchestrator:
         self.n_predict = n_predict
         self.startup_logs = startup_logs or []
         self.t_start = time.time()
+        self._query: dict[str, str] = {}
         self._server: asyncio.AbstractServer | None = None
 
     # ---- tiny HTTP/1.1 layer ------------------------------------------------------------------------
@@ -439,6 +440,111 @@ class Orchestrator:
             await self._server.serve_forever()
 
 
+class ModelRouter(Orchestrator):
+    """Several models behind one port: requests name a model (`"model"` field of the JSON body, default = the first one), models
+    are loaded on first use, at most `max_loaded` stay resident (least recently used idle model is unloaded first) and models
+    idle for `sleep_idle_s` seconds are unloaded to free the GPU.  Each loaded model is a full Orchestrator (own scheduler
+    thread, slots, KV cache), so every route works per model.
+
+    Parity: llama-server's router mode (`tools/server/server-models.cpp:415-600`: spawn / monitor child servers, LRU unload)
+    and `--sleep-idle-seconds` (`server-context.cpp:651-665`); here the models share the process instead of being child
+    processes (the native front-end `runtime/orchestrator.cpp` supervises the process as a whole)."""
+
+    def __init__(self, models: dict[str, str], build_kw: dict | None = None, max_loaded: int = 1, sleep_idle_s: float = 0.0,
+                 static_dir: str = STATIC_DIR, n_predict: int = 200, **orch_kw):
+        super().__init__(None, {"name": "router"}, static_dir, n_predict, api_key=orch_kw.get("api_key"))
+        self.models = dict(models)
+        self.build_kw = build_kw or {}
+        self.max_loaded = max(1, max_loaded)
+        self.sleep_idle_s = sleep_idle_s
+        self.orch_kw = orch_kw
+        self.loaded: dict[str, Orchestrator] = {}
+        self.last_used: dict[str, float] = {}
+        self.n_loads = 0
+        self._load_lock = asyncio.Lock()
+
+    @staticmethod
+    def _busy(o: Orchestrator) -> bool:
+        return bool(o.sched.queue) or any(s.state.name != "IDLE" for s in o.sched.slots)
+
+    def _unload(self, name: str):
+        o = self.loaded.pop(name, None)
+        if o is not None:
+            o.sched.stop()
+            del o
+            import gc
+            import torch
+            gc.collect()
+            if torch.cuda.is_available():
+                torch.cuda.empty_cache()
+
+    def _load(self, name: str) -> Orchestrator:
+        sched, info, logs = build_service(self.models[name], **self.build_kw)
+        sched.start()
+        self.n_loads += 1
+        return Orchestrator(sched, info, self.static_dir, self.n_predict, logs, **self.orch_kw)
+
+    async def acquire(self, name: str) -> Orchestrator:
+        async with self._load_lock:
+            if name not in self.loaded:
+                while len(self.loaded) >= self.max_loaded:
+                    idle = sorted((n for n, o in self.loaded.items() if not self._busy(o)), key=lambda n: self.last_used.get(n, 0.0))
+                    if not idle:
+                        await asyncio.sleep(0.05)      # every resident model is serving: wait for one to drain
+                        continue
+                    self._unload(idle[0])
+                self.loaded[name] = await asyncio.get_running_loop().run_in_executor(None, self._load, name)
+            self.last_used[name] = time.time()
+            return self.loaded[name]
+
+    async def reap_idle(self):
+        """Background task: unload models nobody has used for sleep_idle_s seconds."""
+        while self.sleep_idle_s > 0:
+            await asyncio.sleep(min(1.0, self.sleep_idle_s / 2))
+            async with self._load_lock:
+                now = time.time()
+                for n in [n for n, o in self.loaded.items() if now - self.last_used.get(n, now) > self.sleep_idle_s and not self._busy(o)]:
+                    self._unload(n)
+
+    async def route(self, method, path, headers, body, reader, writer) -> bool:
+        if method == "GET" and path == "/v1/models":
+            await self._json(writer, {"object": "list", "data": [
+                {"id": n, "object": "model", "owned_by": "dlp_b200", "path": p,
+                 "status": "loaded" if n in self.loaded else "unloaded"} for n, p in self.models.items()]})
+            return True
+        if method == "GET" and path == "/health":
+            await self._json(writer, {"status": "ok", "models_loaded": sorted(self.loaded), "loads": self.n_loads})
+            return True
+        if method in ("GET", "HEAD", "OPTIONS") and path not in ("/metrics", "/slots", "/props"):
+            return await super().route(method, path, headers, body, reader, writer)
+        name = next(iter(self.models))
+        if body:
+            try:
+                name = str(json.loads(body).get("model") or name)
+            except (json.JSONDecodeError, AttributeError):
+                pass
+        name = self._query.get("model", name)
+        if name not in self.models:
+            await self._json(writer, {"error": {"code": 404, "message": f"model {name!r} not found", "type": "not_found_error"}}, "404 Not Found")
+            return True
+        orch = await self.acquire(name)
+        orch._query = self._query
+        try:
+            return await orch.route(method, path, headers, body, reader, writer)
+        finally:
+            self.last_used[name] = time.time()
+
+    async def serve(self, host: str = "0.0.0.0", port: int = 3005):
+        reaper = asyncio.ensure_future(self.reap_idle()) if self.sleep_idle_s > 0 else None
+        try:
+            await super().serve(host, port)
+        finally:
+            if reaper:
+                reaper.cancel()
+            for n in list(self.loaded):
+                self._unload(n)
+
+
 def build_service(model: str, device: str = "cuda", n_ctx: int = 2048, n_slots: int = 4, n_batch: int = 2048, page_size: int = 64,
                   lora=None):
     """Load a GGUF checkpoint and return (scheduler, model_info, startup_logs)."""
@@ -468,7 +574,10 @@ def build_service(model: str, device: str = "cuda", n_ctx: int = 2048, n_slots: 
 
 def main(argv=None):
     ap = argparse.ArgumentParser(description="dlp_b200 orchestrator (wire-compatible with the reference's /chat SSE API)")
-    ap.add_argument("-m", "--model", required=True)
+    ap.add_argument("-m", "--model", default=None)
+    ap.add_argument("--models", default=None, help="router mode: comma separated name=path.gguf list (or a directory of .gguf files)")
+    ap.add_argument("--models-max", type=int, default=1, help="router mode: models kept resident at once")
+    ap.add_argument("--sleep-idle-seconds", type=float, default=0.0, help="router mode: unload a model after this many idle seconds")
     ap.add_argument("--host", default=os.environ.get("DLP_HOST", "0.0.0.0"))
     ap.add_argument("--port", type=int, default=int(os.environ.get("DLP_PORT", "3005")))
     ap.add_argument("-c", "--ctx-size", type=int, default=2048)
@@ -483,6 +592,21 @@ def main(argv=None):
     ap.add_argument("--slot-save-path", default=None, help="directory for /slots/{id}?action=save|restore files")
     ap.add_argument("--context-shift", action="store_true", help="slide the context window instead of stopping at n_ctx")
     a = ap.parse_args(argv)
+    if a.models:
+        if os.path.isdir(a.models):
+            models = {os.path.splitext(f)[0]: os.path.join(a.models, f) for f in sorted(os.listdir(a.models)) if f.endswith(".gguf")}
+        else:
+            models = dict(item.split("=", 1) if "=" in item else (os.path.splitext(os.path.basename(item))[0], item) for item in a.models.split(","))
+        router = ModelRouter(models, dict(device=a.device, n_ctx=a.ctx_size, n_slots=a.parallel, n_batch=a.batch_size), a.models_max,
+                             a.sleep_idle_seconds, a.static, a.predict, api_key=a.api_key, max_queue=a.max_queue, slot_save_path=a.slot_save_path)
+        print(f"dlp_b200 router ready: http://localhost:{a.port} ({len(models)} models)", flush=True)
+        try:
+            asyncio.run(router.serve(a.host, a.port))
+        except KeyboardInterrupt:
+            pass
+        return
+    if not a.model:
+        ap.error("-m/--model or --models is required")
     sched, info, logs = build_service(a.model, a.device, a.ctx_size, a.parallel, a.batch_size, lora=lora_from_args(a))
     sched.context_shift = a.context_shift
     sched.start()

@@ -252,3 +252,34 @@ def test_api_key_slot_save_restore_and_templates(tmp_models, tmp_path):
     assert apply_chat_template({"tokenizer.chat_template": "[INST] <<SYS>>"}, msgs) == "[INST] <<SYS>>\nS\n<</SYS>>\n\nU [/INST]"
     assert "<start_of_turn>model" in apply_chat_template({"tokenizer.chat_template": "<start_of_turn>"}, msgs)
     assert apply_chat_template({"tokenizer.chat_template": "<|start_header_id|>"}, msgs).count("<|eot_id|>") == 2
+
+
+def test_model_router_loads_on_demand_and_unloads_lru(tmp_models):
+    from distributed_llm_pipeline_b200.serving.orchestrator import ModelRouter
+    models = {"llama-tiny": tmp_models[("tiny", "F16")], "qwen-tiny": tmp_models[("tiny-qwen2", "F16")]}
+    router = ModelRouter(models, dict(device="cpu", n_ctx=64, n_slots=1, n_batch=32), max_loaded=1, sleep_idle_s=1.0, n_predict=4)
+    port = _serve(router)
+    _, _, body = _http(port, "GET", "/v1/models")
+    assert {m["id"]: m["status"] for m in json.loads(body)["data"]} == {"llama-tiny": "unloaded", "qwen-tiny": "unloaded"}
+    req = lambda m: json.dumps({"model": m, "prompt": "a b c", "n_predict": 3, "temperature": 0}).encode()  # noqa: E731
+    _, _, body = _http(port, "POST", "/completion", req("llama-tiny"))
+    first = json.loads(body)["content"]
+    _, _, body = _http(port, "GET", "/health")
+    assert json.loads(body)["models_loaded"] == ["llama-tiny"]
+    _, _, body = _http(port, "POST", "/completion", req("qwen-tiny"))          # second model evicts the first (max_loaded = 1)
+    assert "content" in json.loads(body)
+    _, _, body = _http(port, "GET", "/health")
+    assert json.loads(body)["models_loaded"] == ["qwen-tiny"]
+    _, _, body = _http(port, "POST", "/completion", req("llama-tiny"))          # reload: same deterministic output
+    assert json.loads(body)["content"] == first
+    st, _, _ = _http(port, "POST", "/completion", req("nope"))
+    assert " 404 " in st
+    _, _, body = _http(port, "GET", "/health")
+    assert json.loads(body)["loads"] == 3
+    deadline = time.time() + 10                                                   # --sleep-idle-seconds: unloaded when idle
+    while time.time() < deadline:
+        _, _, body = _http(port, "GET", "/health")
+        if not json.loads(body)["models_loaded"]:
+            break
+        time.sleep(0.3)
+    assert json.loads(body)["models_loaded"] == []
