@@ -248,7 +248,8 @@ __global__ void __launch_bounds__(256, 2) gemv_dense_v3_kernel(const GemvParams 
     const int g_hi = (int)(((long long)groups_total * (blockIdx.x + 1)) / gridDim.x);
     const int n_units = (g_hi - g_lo) * KC;
 
-    uint4 buf[DEPTH][2][U];   // [ring slot][stream][load]
+    constexpr bool PRE2 = DEPTH == 3;          // experiment: both register sets are requested before the dependency wait
+    uint4 buf[2][2][U];   // [register set][stream][load]
     int roff = 0;         // expert row offset (MoE), known only after the router kernel has finished
     auto issue = [&](int u, int b) {
         const int g = g_lo + u / KC, c = u % KC;
@@ -305,11 +306,12 @@ __global__ void __launch_bounds__(256, 2) gemv_dense_v3_kernel(const GemvParams 
 
     // Two register sets, hand-unrolled (DEPTH == 2): the next unit is requested *before* the current one is reduced.  A generic
     // ring that refills a slot after reducing it measured 8 % slower on the fp16 step (316 vs 345 tok/s), see profiles/.
-    static_assert(DEPTH == 2, "dense v3 is tuned for two register sets");
+    static_assert(DEPTH == 2 || DEPTH == 3, "dense v3 is tuned for two register sets");
     int u = warp;                              // the first round is assigned statically so that it can start right now
-    if (threadIdx.x == 0) next_unit = 8;
+    if (threadIdx.x == 0) next_unit = PRE2 ? 16 : 8;
     const bool dyn_rows = p.row_off_dev != nullptr;
     if (!dyn_rows && u < n_units) issue(u, 0); // weights are static: requested before the predecessor has finished
+    if (PRE2 && !dyn_rows && u + 8 < n_units) issue(u + 8, 1);
     trace_event(p.trace, TR_GEMV | TR_BEGIN);
     trace_event_cta(p.trace, TR_BEGIN);
     pdl_wait();
@@ -322,6 +324,21 @@ __global__ void __launch_bounds__(256, 2) gemv_dense_v3_kernel(const GemvParams 
     const float oscale = p.out_scale_dev ? *p.out_scale_dev : 1.f;
     stage_x<NT>(p, K, xs, red);                // (ends with __syncthreads: next_unit is visible)
 
+    if (PRE2 && u < n_units) {                 // peeled first round: set 1 (unit u + 8) is already in flight
+        const int un = u + 8;
+        if (un < n_units && dyn_rows) issue(un, 1);
+        reduce(u, 0);
+        if (un < n_units) {
+            int u2 = 0;
+            if (lane == 0) u2 = atomicAdd(&next_unit, 1);
+            u2 = __shfl_sync(0xffffffffu, u2, 0);
+            if (u2 < n_units) issue(u2, 0);
+            reduce(un, 1);
+            u = u2;
+        } else {
+            u = n_units;
+        }
+    }
     while (u < n_units) {                      // software pipeline, unrolled by two for static register indexing
         int un = 0;
         if (lane == 0) un = atomicAdd(&next_unit, 1);
@@ -1034,11 +1051,13 @@ int gemv(const GemvParams& p_in, int wtype, cudaStream_t stream) {
         if (v3_cfg == 1 && U == 4) U = 2;
         const bool bf = wtype == W_BF16;
         const size_t xsm = smem;
+        static int pre2 = -1;
+        if (pre2 < 0) { const char* e = getenv("DLP_GEMV_PRE2"); pre2 = (e && e[0] == '1') ? 1 : 0; }
 #define DLP_V3(NT_, U_, D_)                                                                                       \
     return bf ? launch_gemv_v3(gemv_dense_v3_kernel<NT_, true, U_, D_>, p, U_, xsm, stream)                        \
               : launch_gemv_v3(gemv_dense_v3_kernel<NT_, false, U_, D_>, p, U_, xsm, stream);
 #define DLP_V3_T(NT_)                                                                                             \
-    if (U == 4) { DLP_V3(NT_, 4, 2) } else if (U == 2) { DLP_V3(NT_, 2, 2) } else { DLP_V3(NT_, 1, 2) }
+    if (U == 4) { if (pre2) { DLP_V3(NT_, 4, 3) } else { DLP_V3(NT_, 4, 2) } } else if (U == 2) { DLP_V3(NT_, 2, 2) } else { DLP_V3(NT_, 1, 2) }
         if (xsm + 8192 <= 100 * 1024) {   // x (+ partials) must fit next to a second resident CTA
             if (T == 1) { DLP_V3_T(1) }
             if (T == 2) { DLP_V3_T(2) }
