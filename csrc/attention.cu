@@ -620,9 +620,9 @@ __global__ void __launch_bounds__(128) attn_prefill_kernel(const __half* __restr
     constexpr int BQ = 64, BKV = 64;
     extern __shared__ __align__(16) uint8_t att_smem[];
     __half* sQ = reinterpret_cast<__half*>(att_smem);
-    __half* sK = sQ + BQ * LD;
-    __half* sV = sK + BKV * LD;
-    const int q0 = blockIdx.x * BQ, hq = blockIdx.y, kvh = hq / (Hq / Hkv);
+    __half* sKV = sQ + BQ * LD;              // two stages of (K tile | V tile): the next tile lands while this one is consumed
+    // heaviest query tiles first: under the causal mask the last tile has the most key tiles to walk
+    const int q0 = ((int)gridDim.x - 1 - (int)blockIdx.x) * BQ, hq = blockIdx.y, kvh = hq / (Hq / Hkv);
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int g = lane >> 2, t4 = lane & 3;
     constexpr int CPR = D / 8;  // 16-byte chunks per row
@@ -642,19 +642,27 @@ __global__ void __launch_bounds__(128) attn_prefill_kernel(const __half* __restr
     float m_run[2] = {-INFINITY, -INFINITY}, l_run[2] = {0.f, 0.f};
     constexpr float LOG2E = 1.4426950408889634f;
 
-    for (int kt = 0; kt < n_tiles; ++kt) {
-        __syncthreads();  // previous tile fully consumed
+    auto load_kv = [&](int kt) {
+        __half* dK = sKV + (kt & 1) * 2 * BKV * LD;
+        __half* dV = dK + BKV * LD;
         for (int i = tid; i < BKV * CPR; i += 128) {
             const int r = i / CPR, c = i % CPR;
             const int tok = kt * BKV + r;
             const bool ok = tok < n_kv;
             const int tk = ok ? tok : 0;
             const size_t src = (((size_t)bt[tk / PS] * Hkv + kvh) * PS + tk % PS) * D + c * 8;
-            cp_async16(sK + r * LD + c * 8, kc + src, ok);
-            cp_async16(sV + r * LD + c * 8, vc + src, ok);
+            cp_async16(dK + r * LD + c * 8, kc + src, ok);
+            cp_async16(dV + r * LD + c * 8, vc + src, ok);
         }
-        cp_async_wait_all();
-        __syncthreads();
+        cp_async_commit();
+    };
+    load_kv(0);                                // (commits the Q rows requested above with it)
+    for (int kt = 0; kt < n_tiles; ++kt) {
+        __syncthreads();                       // tile kt-1 fully consumed: its stage may be refilled
+        if (kt + 1 < n_tiles) { load_kv(kt + 1); cp_async_wait_group<1>(); } else { cp_async_wait_group<0>(); }
+        __syncthreads();                       // tile kt (and Q) visible to every warp
+        const __half* sK = sKV + (kt & 1) * 2 * BKV * LD;
+        const __half* sV = sK + BKV * LD;
         if (kt == 0) {
 #pragma unroll
             for (int ks = 0; ks < D / 16; ++ks)
@@ -759,12 +767,14 @@ int attn_prefill(const __half* q, const __half* kc, const __half* vc, const int*
     DLP_REQUIRE(T > 0 && Hq % Hkv == 0, "attn_prefill: bad shape");
     dim3 grid((T + 63) / 64, Hq);
     if (D == 128) {
-        const int smem = 3 * 64 * (128 + 8) * 2;
+        const int smem = 5 * 64 * (128 + 8) * 2;   // Q + 2 stages x (K, V)
         static bool cfg = false;
         if (!cfg) { DLP_CHECK_CUDA(cudaFuncSetAttribute(attn_prefill_kernel<128>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem)); cfg = true; }
         attn_prefill_kernel<128><<<grid, 128, smem, s>>>(q, kc, vc, bt_row, out, T, pos0, Hq, Hkv, page_size);
     } else if (D == 64) {
-        const int smem = 3 * 64 * (64 + 8) * 2;
+        const int smem = 5 * 64 * (64 + 8) * 2;
+        static bool cfg64 = false;
+        if (!cfg64) { DLP_CHECK_CUDA(cudaFuncSetAttribute(attn_prefill_kernel<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem)); cfg64 = true; }
         attn_prefill_kernel<64><<<grid, 128, smem, s>>>(q, kc, vc, bt_row, out, T, pos0, Hq, Hkv, page_size);
     } else {
         DLP_REQUIRE(false, "attn_prefill: head dim %d unsupported (64, 128)", D);
