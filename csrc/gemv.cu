@@ -232,6 +232,7 @@ __global__ void __launch_bounds__(256, 2) gemv_dense_v3_kernel(const GemvParams 
     const int K = p.w0.K, N = p.w0.N;
     constexpr int KCW = 256 * U;               // columns per unit
     const int KC = K / KCW;                    // K chunks per row (host guarantees divisibility)
+    const unsigned kc_inv = (unsigned)((0x100000000ull + (unsigned)KC - 1) / (unsigned)KC);
     const bool dual = p.out_mode == GV_SWIGLU_F16;
     const int rpu = dual ? 1 : 2;              // rows per unit (dual: one gate row + the matching up row)
     __half* xs = reinterpret_cast<__half*>(gv_smem);
@@ -252,7 +253,8 @@ __global__ void __launch_bounds__(256, 2) gemv_dense_v3_kernel(const GemvParams 
     uint4 buf[2][2][U];   // [register set][stream][load]
     int roff = 0;         // expert row offset (MoE), known only after the router kernel has finished
     auto issue = [&](int u, int b) {
-        const int g = g_lo + u / KC, c = u % KC;
+        const int gq = KC == 1 ? u : (int)__umulhi((unsigned)u, kc_inv);   // u / KC without the integer-division sequence
+        const int g = g_lo + gq, c = u - gq * KC;
         const int row = g * rpu;
         const uint8_t* s0 = p.w0.base + ((size_t)(row + roff) * K + (size_t)c * KCW + lane * 8) * 2;
         const uint8_t* s1 = dual ? p.w1.base + ((size_t)(row + roff) * K + (size_t)c * KCW + lane * 8) * 2
@@ -264,7 +266,7 @@ __global__ void __launch_bounds__(256, 2) gemv_dense_v3_kernel(const GemvParams 
         }
     };
     auto reduce = [&](int u, int b) {
-        const int g = u / KC, c = u % KC;
+        const int g = KC == 1 ? u : (int)__umulhi((unsigned)u, kc_inv), c = u - g * KC;
         float acc[2][NT];
 #pragma unroll
         for (int m = 0; m < 2; ++m)
@@ -673,8 +675,11 @@ __global__ void __launch_bounds__(256) gemv_quant_kernel(const GemvParams p) {
 // results, or the warp would stall for a full memory latency per unit); all decoding happens in qraw_dot().
 template <int WT> struct QRaw;
 template <> struct QRaw<W_Q8_0> { uint4 a, b; unsigned short d; };
-template <> struct QRaw<W_Q4_K> { uint4 hdr, qs; };
-template <> struct QRaw<W_Q5_K> { uint4 hdr, qs, qh; };
+// K-quants 4/5: one lane owns a whole 64-weight group (32 bytes of nibbles = sub-blocks 2j | 2j+1 of a super-block), so the two
+// 6-bit scales / mins are decoded once per 64 weights and the per-unit overhead (warp sums, queue, partials) is halved
+template <> struct QRaw<W_Q4_K> { uint4 hdr, qs0, qs1; };
+template <> struct QRaw<W_Q5_K> { uint4 hdr, qs0, qs1, qh0, qh1; };
+template <int WT> struct QChunkW { static constexpr int value = (WT == W_Q4_K || WT == W_Q5_K) ? 64 : 32; };   // weights per lane-chunk
 template <> struct QRaw<W_Q6_K> { uint4 ql, qh; unsigned short d; signed char s0, s1; };
 
 template <int WT> __device__ __forceinline__ void qraw_load(const QWeight& w, int row, int c, QRaw<WT>& r);
@@ -685,17 +690,20 @@ template <> __device__ __forceinline__ void qraw_load<W_Q8_0>(const QWeight& w, 
     r.d = __ldg(reinterpret_cast<const unsigned short*>(w.aux0) + (size_t)row * (w.K >> 5) + c);
 }
 template <> __device__ __forceinline__ void qraw_load<W_Q4_K>(const QWeight& w, int row, int c, QRaw<W_Q4_K>& r) {
-    const int blk = c >> 3, j = (c & 7) >> 1, l0 = (c & 1) * 16;
+    const int blk = c >> 2, j = c & 3;           // c counts 64-weight groups
     const uint8_t* b = w.base + ((size_t)row * (w.K >> 8) + blk) * 144;
     r.hdr = __ldg(reinterpret_cast<const uint4*>(b));
-    r.qs = ldg_nc_v4(b + 16 + j * 32 + l0);
+    r.qs0 = ldg_nc_v4(b + 16 + j * 32);
+    r.qs1 = ldg_nc_v4(b + 16 + j * 32 + 16);
 }
 template <> __device__ __forceinline__ void qraw_load<W_Q5_K>(const QWeight& w, int row, int c, QRaw<W_Q5_K>& r) {
-    const int blk = c >> 3, j = (c & 7) >> 1, l0 = (c & 1) * 16;
+    const int blk = c >> 2, j = c & 3;
     const uint8_t* b = w.base + ((size_t)row * (w.K >> 8) + blk) * 176;
     r.hdr = __ldg(reinterpret_cast<const uint4*>(b));
-    r.qh = __ldg(reinterpret_cast<const uint4*>(b + 16 + l0));
-    r.qs = ldg_nc_v4(b + 48 + j * 32 + l0);
+    r.qh0 = __ldg(reinterpret_cast<const uint4*>(b + 16));
+    r.qh1 = __ldg(reinterpret_cast<const uint4*>(b + 32));
+    r.qs0 = ldg_nc_v4(b + 48 + j * 32);
+    r.qs1 = ldg_nc_v4(b + 48 + j * 32 + 16);
 }
 template <> __device__ __forceinline__ void qraw_load<W_Q6_K>(const QWeight& w, int row, int c, QRaw<W_Q6_K>& r) {
     const int blk = c >> 3, cc = c & 7, half = cc >> 2, l0 = (cc & 3) * 16;
@@ -715,7 +723,7 @@ template <int WT> __device__ __forceinline__ void chunk_offsets(int c, int& k0, 
     else if (WT == W_Q6_K) {
         const int blk = c >> 3, cc = c & 7, half = cc >> 2, l0 = (cc & 3) * 16;
         k0 = blk * 256 + half * 128 + (l0 >> 5) * 32 + (l0 & 31); k1 = k0 + 64;
-    } else { k0 = (c >> 3) * 256 + ((c & 7) >> 1) * 64 + (c & 1) * 16; k1 = k0 + 32; }
+    } else { k0 = (c >> 2) * 256 + (c & 3) * 64; k1 = k0 + 32; }   // 64-weight group: low-nibble sub-block at k0, high at k0 + 32
 }
 
 __device__ __forceinline__ int dp4a4(const uint32_t (&q)[4], const uint4& x) {
@@ -727,46 +735,58 @@ __device__ __forceinline__ int dp4a4(const uint32_t (&q)[4], const uint4& x) {
 
 __device__ __forceinline__ float us2f(unsigned short h) { return __half2float(__ushort_as_half(h)); }
 
-// dot of one raw chunk with token t's int8 activations; xq int8 [K], xd fp32 [K/32] scales, xs16 fp32 [K/16] exact sums.
-// `c` is the chunk index (needed to pick the sub-block scales).  Unsigned quant values are centred before the integer dot
-// ( sum (q-z) xq = dp4a(q, xq) - z * dp4a(1, xq) ), which keeps the activation-rounding noise off the large offset term.
+// dot of one raw chunk with token t's int8 activations; xq int8 [K], xd fp32 [K/32] scales, xs16 fp32 [K/16] exact sums,
+// xqs16 int [K/16] sums of the int8 values.  `c` is the chunk index (needed to pick the sub-block scales).  Unsigned quant
+// values are centred ( sum (q-z) xq = dp4a(q, xq) - z * sum xq ), which keeps the activation-rounding noise off the large offset
+// term; the sum of xq per 16 values comes from the prologue instead of a second set of dp4a per chunk.
 template <int WT>
-__device__ __forceinline__ float qraw_dot(const QRaw<WT>& r, const int8_t* xq, const float* xd, const float* xs16, int c, int k0, int k1) {
-    const uint4 xa = *reinterpret_cast<const uint4*>(xq + k0);
-    const uint4 xb = *reinterpret_cast<const uint4*>(xq + k1);
-    const uint32_t ones[4] = {0x01010101u, 0x01010101u, 0x01010101u, 0x01010101u};
+__device__ __forceinline__ float qraw_dot(const QRaw<WT>& r, const int8_t* xq, const float* xd, const float* xs16, const int* xqs16,
+                                          int c, int k0, int k1) {
     if constexpr (WT == W_Q8_0) {
+        const uint4 xa = *reinterpret_cast<const uint4*>(xq + k0);
+        const uint4 xb = *reinterpret_cast<const uint4*>(xq + k1);
         const uint32_t qa[4] = {r.a.x, r.a.y, r.a.z, r.a.w}, qb[4] = {r.b.x, r.b.y, r.b.z, r.b.w};
         const int isum = dp4a4(qa, xa) + dp4a4(qb, xb);
         return us2f(r.d) * xd[k0 >> 5] * (float)isum;
     } else if constexpr (WT == W_Q4_K || WT == W_Q5_K) {
-        const int j = (c & 7) >> 1;
+        const int j = c & 3;
+        const int rot = (c >> 1) & 3;                      // granule rotation of this 64-byte group (see the quantise prologue)
+        const int8_t* xg = xq + k0;
+        const uint4 xa0 = *reinterpret_cast<const uint4*>(xg + ((rot & 3) << 4)), xa1 = *reinterpret_cast<const uint4*>(xg + (((1 + rot) & 3) << 4));
+        const uint4 xb0 = *reinterpret_cast<const uint4*>(xg + (((2 + rot) & 3) << 4)), xb1 = *reinterpret_cast<const uint4*>(xg + (((3 + rot) & 3) << 4));
         const float2 dm = h2_to_f2(r.hdr.x);
         int sc0, mn0, sc1, mn1;
         scale_min_k4(r.hdr.y, r.hdr.z, r.hdr.w, 2 * j, sc0, mn0);
         scale_min_k4(r.hdr.y, r.hdr.z, r.hdr.w, 2 * j + 1, sc1, mn1);
         const float s0 = dm.x * sc0, s1 = dm.x * sc1;
-        const uint32_t w4[4] = {r.qs.x, r.qs.y, r.qs.z, r.qs.w};
-        uint32_t lo[4], hi[4];
+        const uint32_t w0[4] = {r.qs0.x, r.qs0.y, r.qs0.z, r.qs0.w}, w1[4] = {r.qs1.x, r.qs1.y, r.qs1.z, r.qs1.w};
+        uint32_t lo0[4], hi0[4], lo1[4], hi1[4];
 #pragma unroll
         for (int i = 0; i < 4; ++i) {
-            lo[i] = w4[i] & 0x0F0F0F0Fu;
-            hi[i] = (w4[i] >> 4) & 0x0F0F0F0Fu;
+            lo0[i] = w0[i] & 0x0F0F0F0Fu;
+            hi0[i] = (w0[i] >> 4) & 0x0F0F0F0Fu;
+            lo1[i] = w1[i] & 0x0F0F0F0Fu;
+            hi1[i] = (w1[i] >> 4) & 0x0F0F0F0Fu;
         }
         constexpr int Z = (WT == W_Q5_K) ? 16 : 8;
         if constexpr (WT == W_Q5_K) {
-            const uint32_t h4[4] = {r.qh.x, r.qh.y, r.qh.z, r.qh.w};
+            const uint32_t h0[4] = {r.qh0.x, r.qh0.y, r.qh0.z, r.qh0.w}, h1[4] = {r.qh1.x, r.qh1.y, r.qh1.z, r.qh1.w};
 #pragma unroll
             for (int i = 0; i < 4; ++i) {
-                lo[i] |= ((h4[i] >> (2 * j)) & 0x01010101u) << 4;
-                hi[i] |= ((h4[i] >> (2 * j + 1)) & 0x01010101u) << 4;
+                lo0[i] |= ((h0[i] >> (2 * j)) & 0x01010101u) << 4;
+                hi0[i] |= ((h0[i] >> (2 * j + 1)) & 0x01010101u) << 4;
+                lo1[i] |= ((h1[i] >> (2 * j)) & 0x01010101u) << 4;
+                hi1[i] |= ((h1[i] >> (2 * j + 1)) & 0x01010101u) << 4;
             }
         }
-        const int ia = dp4a4(lo, xa) - Z * dp4a4(ones, xa);
-        const int ib = dp4a4(hi, xb) - Z * dp4a4(ones, xb);
+        const int ka = k0 >> 4, kb = k1 >> 4;
+        const int ia = dp4a4(lo0, xa0) + dp4a4(lo1, xa1) - Z * (xqs16[ka] + xqs16[ka + 1]);
+        const int ib = dp4a4(hi0, xb0) + dp4a4(hi1, xb1) - Z * (xqs16[kb] + xqs16[kb + 1]);
         const float b0 = (float)Z * s0 - dm.y * mn0, b1 = (float)Z * s1 - dm.y * mn1;
-        return s0 * xd[k0 >> 5] * (float)ia + s1 * xd[k1 >> 5] * (float)ib + b0 * xs16[k0 >> 4] + b1 * xs16[k1 >> 4];
+        return s0 * xd[k0 >> 5] * (float)ia + s1 * xd[k1 >> 5] * (float)ib + b0 * (xs16[ka] + xs16[ka + 1]) + b1 * (xs16[kb] + xs16[kb + 1]);
     } else {   // Q6_K: stored value = q + 32
+        const uint4 xa = *reinterpret_cast<const uint4*>(xq + k0);
+        const uint4 xb = *reinterpret_cast<const uint4*>(xq + k1);
         const int sh = (((c & 7) & 3) * 16 >> 5) * 2;
         const uint32_t l4[4] = {r.ql.x, r.ql.y, r.ql.z, r.ql.w}, h4[4] = {r.qh.x, r.qh.y, r.qh.z, r.qh.w};
         uint32_t lo[4], hi[4];
@@ -775,8 +795,8 @@ __device__ __forceinline__ float qraw_dot(const QRaw<WT>& r, const int8_t* xq, c
             lo[i] = (l4[i] & 0x0F0F0F0Fu) | (((h4[i] >> sh) & 0x03030303u) << 4);
             hi[i] = ((l4[i] >> 4) & 0x0F0F0F0Fu) | (((h4[i] >> (sh + 4)) & 0x03030303u) << 4);
         }
-        const int ia = dp4a4(lo, xa) - 32 * dp4a4(ones, xa);
-        const int ib = dp4a4(hi, xb) - 32 * dp4a4(ones, xb);
+        const int ia = dp4a4(lo, xa) - 32 * xqs16[k0 >> 4];
+        const int ib = dp4a4(hi, xb) - 32 * xqs16[k1 >> 4];
         const float d = us2f(r.d);
         return d * (float)r.s0 * xd[k0 >> 5] * (float)ia + d * (float)r.s1 * xd[k1 >> 5] * (float)ib;
     }
@@ -786,19 +806,24 @@ template <int WT, int NT>
 __global__ void __launch_bounds__(256, 2) gemv_quant_v3_kernel(const GemvParams p) {
     extern __shared__ __align__(16) uint8_t gv_smem[];
     const int K = p.w0.K, N = p.w0.N;
-    const int nchunk = K >> 5;
-    const int KC = (nchunk + 31) >> 5;          // units of 32 chunks (1024 columns) per row; the last may be partial
+    constexpr int CW = QChunkW<WT>::value;       // weights per lane-chunk (32, or 64 for the 4/5-bit K-quants)
+    const int nchunk = K / CW;
+    const int nb32 = K >> 5;                    // 32-value activation blocks per token
+    const int KC = (nchunk + 31) >> 5;          // units of 32 chunks (1024 or 2048 columns) per row; the last may be partial
+    const unsigned kc_inv = (unsigned)((0x100000000ull + (unsigned)KC - 1) / (unsigned)KC);   // exact for u < 2^32 / KC (KC == 1 is special-cased: the reciprocal would not fit)
     const bool dual = p.out_mode == GV_SWIGLU_F16;
     const int rpu = dual ? 1 : 2;
-    // shared memory: fp16 x [NT][K] (stage_x output, AR staging behind it) | int8 xq [NT][K] | xd [NT][K/32] | xs16 [NT][K/16] | partials
+    // shared memory: fp16 x [NT][K] (stage_x output, AR staging behind it) | int8 xq [NT][K] | xd [NT][K/32] | xs16 [NT][K/16] | xqs16 [NT][K/16] | partials
     __half* xs = reinterpret_cast<__half*>(gv_smem);
     size_t off = (size_t)NT * K * 2 + (p.ar_in.buf ? (size_t)K * 4 : 0);
     off = (off + 15) & ~size_t(15);
     int8_t* xq = reinterpret_cast<int8_t*>(gv_smem + off);
     off += (size_t)NT * K;
     float* xd = reinterpret_cast<float*>(gv_smem + off);
-    off += (size_t)NT * nchunk * 4;
+    off += (size_t)NT * nb32 * 4;
     float* xs16 = reinterpret_cast<float*>(gv_smem + off);
+    off += (size_t)NT * (K >> 4) * 4;
+    int* xqs16 = reinterpret_cast<int*>(gv_smem + off);
     off += (size_t)NT * (K >> 4) * 4;
     float* partial = reinterpret_cast<float*>(gv_smem + off);
     __shared__ float red[32];
@@ -809,11 +834,12 @@ __global__ void __launch_bounds__(256, 2) gemv_quant_v3_kernel(const GemvParams 
     const int g_hi = (int)(((long long)groups_total * (blockIdx.x + 1)) / gridDim.x);
     const int n_units = (g_hi - g_lo) * KC;
 
-    constexpr int DEPTH = sizeof(QRaw<WT>) >= 36 ? 3 : 4;   // units in flight per warp (ncu: two were not enough to cover HBM latency, 1.5-3.3 TB/s)
+    constexpr int DEPTH = sizeof(QRaw<WT>) >= 64 ? 2 : sizeof(QRaw<WT>) >= 36 ? (NT > 1 ? 2 : 3) : 4;   // units in flight per warp (ncu: two were not enough to cover HBM latency, 1.5-3.3 TB/s)
     QRaw<WT> buf[DEPTH][2];   // [ring slot][row stream]
     int roff = 0;             // expert row offset (MoE)
     auto issue = [&](int u, int b) {
-        const int g = g_lo + u / KC, c = (u % KC) * 32 + lane;
+        const int gq = KC == 1 ? u : (int)__umulhi((unsigned)u, kc_inv);   // u / KC without the ~20-instruction integer division
+        const int g = g_lo + gq, c = (u - gq * KC) * 32 + lane;
         if (c >= nchunk) return;
         const int row = g * rpu;
         qraw_load<WT>(p.w0, row + roff, c, buf[b][0]);
@@ -821,7 +847,7 @@ __global__ void __launch_bounds__(256, 2) gemv_quant_v3_kernel(const GemvParams 
         else qraw_load<WT>(p.w0, min(row + 1, N - 1) + roff, c, buf[b][1]);
     };
     auto reduce = [&](int u, int b) {
-        const int g = u / KC, cu = u % KC, c = cu * 32 + lane;
+        const int g = KC == 1 ? u : (int)__umulhi((unsigned)u, kc_inv), cu = u - g * KC, c = cu * 32 + lane;
         float acc[2][NT];
 #pragma unroll
         for (int m = 0; m < 2; ++m)
@@ -832,8 +858,8 @@ __global__ void __launch_bounds__(256, 2) gemv_quant_v3_kernel(const GemvParams 
             chunk_offsets<WT>(c, k0, k1);
 #pragma unroll
             for (int t = 0; t < NT; ++t) {
-                acc[0][t] = qraw_dot<WT>(buf[b][0], xq + (size_t)t * K, xd + (size_t)t * nchunk, xs16 + (size_t)t * (K >> 4), c, k0, k1);
-                acc[1][t] = qraw_dot<WT>(buf[b][1], xq + (size_t)t * K, xd + (size_t)t * nchunk, xs16 + (size_t)t * (K >> 4), c, k0, k1);
+                acc[0][t] = qraw_dot<WT>(buf[b][0], xq + (size_t)t * K, xd + (size_t)t * nb32, xs16 + (size_t)t * (K >> 4), xqs16 + (size_t)t * (K >> 4), c, k0, k1);
+                acc[1][t] = qraw_dot<WT>(buf[b][1], xq + (size_t)t * K, xd + (size_t)t * nb32, xs16 + (size_t)t * (K >> 4), xqs16 + (size_t)t * (K >> 4), c, k0, k1);
             }
         }
         float* dst = partial + ((size_t)g * KC + cu) * 2 * NT;
@@ -876,9 +902,20 @@ __global__ void __launch_bounds__(256, 2) gemv_quant_v3_kernel(const GemvParams 
         s4 += __shfl_xor_sync(0xffffffffu, s4, 2);           // sum over 16 values (4 threads)
         const float d = amax / 127.f, inv = amax > 0.f ? 127.f / amax : 0.f;
         const int q0 = __float2int_rn(a.x * inv), q1 = __float2int_rn(a.y * inv), q2 = __float2int_rn(b.x * inv), q3 = __float2int_rn(b.y * inv);
-        reinterpret_cast<uint32_t*>(xq)[i] = (uint32_t)(q0 & 0xff) | ((uint32_t)(q1 & 0xff) << 8) | ((uint32_t)(q2 & 0xff) << 16) | ((uint32_t)(q3 & 0xff) << 24);
+        // (4/5-bit K-quants read 64 contiguous bytes per lane: the 16-byte granules of every 64-byte group are rotated by
+        //  (group >> 1) & 3 so that the 32 lanes of one load instruction spread over all banks instead of two)
+        int wi = i;
+        if (CW == 64) {
+            const int t = i / (K >> 2), e = i - t * (K >> 2);           // token, word index inside the token
+            const int grp = e >> 4, gran = (e >> 2) & 3, w = e & 3;     // 64-byte group, 16-byte granule, word
+            wi = t * (K >> 2) + (grp << 4) + (((gran + (grp >> 1)) & 3) << 2) + w;
+        }
+        reinterpret_cast<uint32_t*>(xq)[wi] = (uint32_t)(q0 & 0xff) | ((uint32_t)(q1 & 0xff) << 8) | ((uint32_t)(q2 & 0xff) << 16) | ((uint32_t)(q3 & 0xff) << 24);
+        int qs4 = q0 + q1 + q2 + q3;
+        qs4 += __shfl_xor_sync(0xffffffffu, qs4, 1);
+        qs4 += __shfl_xor_sync(0xffffffffu, qs4, 2);         // integer sum over the same 16 values
         if ((i & 7) == 0) xd[i >> 3] = d;
-        if ((i & 3) == 0) xs16[i >> 2] = s4;
+        if ((i & 3) == 0) { xs16[i >> 2] = s4; xqs16[i >> 2] = qs4; }
     }
     __syncthreads();
 
@@ -925,7 +962,7 @@ __global__ void __launch_bounds__(256, 2) gemv_quant_v3_kernel(const GemvParams 
 }
 
 template <typename Kern>
-static int launch_gemv_qv3(Kern kern, const GemvParams& p, size_t x_smem, cudaStream_t stream) {
+static int launch_gemv_qv3(Kern kern, const GemvParams& p, size_t x_smem, cudaStream_t stream, int chunk_w = 32) {
     static thread_local const void* configured[32];
     static thread_local int n_configured = 0;
     bool seen = false;
@@ -939,9 +976,9 @@ static int launch_gemv_qv3(Kern kern, const GemvParams& p, size_t x_smem, cudaSt
     const int groups = (p.w0.N + rpu - 1) / rpu;
     int blocks = sm_count() * 2;
     if (blocks > groups) blocks = groups;
-    const int K = p.w0.K, KC = ((K >> 5) + 31) >> 5;
+    const int K = p.w0.K, KC = ((K / chunk_w) + 31) >> 5;
     const int max_groups = (groups + blocks - 1) / blocks + 1;
-    const size_t smem = ((x_smem + 15) & ~size_t(15)) + (size_t)p.T * (K + (K >> 5) * 4 + (K >> 4) * 4) + (size_t)max_groups * KC * 2 * p.T * sizeof(float);
+    const size_t smem = ((x_smem + 15) & ~size_t(15)) + (size_t)p.T * (K + (K >> 5) * 4 + (K >> 4) * 8) + (size_t)max_groups * KC * 2 * p.T * sizeof(float);
     if (smem > 100 * 1024) return -2;   // caller falls back to v1
     DLP_CHECK_CUDA(launch_pdl(kern, dim3(blocks), dim3(256), smem, stream, p));
     return 0;
@@ -1073,9 +1110,9 @@ int gemv(const GemvParams& p_in, int wtype, cudaStream_t stream) {
         int rc = -2;
 #define DLP_QV3(WT_)                                                                                       \
     case WT_:                                                                                              \
-        rc = T == 1 ? launch_gemv_qv3(gemv_quant_v3_kernel<WT_, 1>, p, xsm, stream)                        \
-           : T == 2 ? launch_gemv_qv3(gemv_quant_v3_kernel<WT_, 2>, p, xsm, stream)                        \
-                    : launch_gemv_qv3(gemv_quant_v3_kernel<WT_, 4>, p, xsm, stream);                       \
+        rc = T == 1 ? launch_gemv_qv3(gemv_quant_v3_kernel<WT_, 1>, p, xsm, stream, QChunkW<WT_>::value)   \
+           : T == 2 ? launch_gemv_qv3(gemv_quant_v3_kernel<WT_, 2>, p, xsm, stream, QChunkW<WT_>::value)   \
+                    : launch_gemv_qv3(gemv_quant_v3_kernel<WT_, 4>, p, xsm, stream, QChunkW<WT_>::value);  \
         break;
         switch (wtype) { DLP_QV3(W_Q8_0) DLP_QV3(W_Q4_K) DLP_QV3(W_Q5_K) DLP_QV3(W_Q6_K) }
 #undef DLP_QV3

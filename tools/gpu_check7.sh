@@ -1,6 +1,4 @@
 #!/usr/bin/env bash
 mkdir -p gpurun_out
-timeout 600 python -m pytest tests/test_kernels_gpu.py -k "prefill" -x -q 2>&1 | tail -3
-timeout 600 python -m pytest tests/test_engine_gpu.py -x -q 2>&1 | tail -3
-python bench.py --steps 32 --warmup 4 2>/dev/null | grep '^{' | python -c "import sys,json; d=json.loads(sys.stdin.read()); print('F16 tg', d['value'], 'tok/s  prefill', d['prefill_tok_s'])"
-python bench.py --ftype Q8_0 --steps 32 --warmup 4 2>/dev/null | grep '^{' | python -c "import sys,json; d=json.loads(sys.stdin.read()); print('Q8_0 tg', d['value'], 'tok/s  prefill', d['prefill_tok_s'])"
+timeout 900 python -m pytest tests -m gpu -x -q 2>&1 | tail -4
+for Q in Q4_K_M Q8_0; do python bench.py --ftype $Q --steps 128 --warmup 16 2>/dev/null | grep '^{' > gpurun_out/bench_$Q.json; python -c "import json; d=json.load(open('gpurun_out/bench_$Q.json')); print('$Q tg', d['value'], 'tok/s', d['ms_per_step'], 'ms  prefill', d['prefill_tok_s'], 'e2e', d['e2e']['value'])"; done
