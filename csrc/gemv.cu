@@ -674,20 +674,22 @@ __global__ void __launch_bounds__(256) gemv_quant_kernel(const GemvParams p) {
 // Raw register images of one 32-weight chunk.  qraw_load() only *issues* loads (no instruction may depend on their
 // results, or the warp would stall for a full memory latency per unit); all decoding happens in qraw_dot().
 template <int WT> struct QRaw;
-template <> struct QRaw<W_Q8_0> { uint4 a, b; unsigned short d; };
+template <> struct QRaw<W_Q8_0> { uint4 a, b, c, e; unsigned d2; };     // 64 int8 weights + their two fp16 block scales
 // K-quants 4/5: one lane owns a whole 64-weight group (32 bytes of nibbles = sub-blocks 2j | 2j+1 of a super-block), so the two
 // 6-bit scales / mins are decoded once per 64 weights and the per-unit overhead (warp sums, queue, partials) is halved
 template <> struct QRaw<W_Q4_K> { uint4 hdr, qs0, qs1; };
 template <> struct QRaw<W_Q5_K> { uint4 hdr, qs0, qs1, qh0, qh1; };
-template <int WT> struct QChunkW { static constexpr int value = (WT == W_Q4_K || WT == W_Q5_K) ? 64 : 32; };   // weights per lane-chunk
+template <int WT> struct QChunkW { static constexpr int value = (WT == W_Q4_K || WT == W_Q5_K || WT == W_Q8_0) ? 64 : 32; };   // weights per lane-chunk
 template <> struct QRaw<W_Q6_K> { uint4 ql, qh; unsigned short d; signed char s0, s1; };
 
 template <int WT> __device__ __forceinline__ void qraw_load(const QWeight& w, int row, int c, QRaw<WT>& r);
 template <> __device__ __forceinline__ void qraw_load<W_Q8_0>(const QWeight& w, int row, int c, QRaw<W_Q8_0>& r) {
-    const uint8_t* qs = w.base + (size_t)row * w.K + (size_t)c * 32;
+    const uint8_t* qs = w.base + (size_t)row * w.K + (size_t)c * 64;          // c counts 64-weight groups (two Q8_0 blocks)
     r.a = ldg_nc_v4(qs);
     r.b = ldg_nc_v4(qs + 16);
-    r.d = __ldg(reinterpret_cast<const unsigned short*>(w.aux0) + (size_t)row * (w.K >> 5) + c);
+    r.c = ldg_nc_v4(qs + 32);
+    r.e = ldg_nc_v4(qs + 48);
+    r.d2 = __ldg(reinterpret_cast<const unsigned*>(w.aux0) + (((size_t)row * (w.K >> 5)) >> 1) + c);
 }
 template <> __device__ __forceinline__ void qraw_load<W_Q4_K>(const QWeight& w, int row, int c, QRaw<W_Q4_K>& r) {
     const int blk = c >> 2, j = c & 3;           // c counts 64-weight groups
@@ -719,7 +721,7 @@ template <> __device__ __forceinline__ void qraw_load<W_Q6_K>(const QWeight& w, 
 
 // element offsets of the two 16-element groups of chunk c (same mapping as load_chunk in quant.cuh)
 template <int WT> __device__ __forceinline__ void chunk_offsets(int c, int& k0, int& k1) {
-    if (WT == W_Q8_0) { k0 = c * 32; k1 = k0 + 16; }
+    if (WT == W_Q8_0) { k0 = c * 64; k1 = k0 + 32; }
     else if (WT == W_Q6_K) {
         const int blk = c >> 3, cc = c & 7, half = cc >> 2, l0 = (cc & 3) * 16;
         k0 = blk * 256 + half * 128 + (l0 >> 5) * 32 + (l0 & 31); k1 = k0 + 64;
@@ -743,11 +745,15 @@ template <int WT>
 __device__ __forceinline__ float qraw_dot(const QRaw<WT>& r, const int8_t* xq, const float* xd, const float* xs16, const int* xqs16,
                                           int c, int k0, int k1) {
     if constexpr (WT == W_Q8_0) {
-        const uint4 xa = *reinterpret_cast<const uint4*>(xq + k0);
-        const uint4 xb = *reinterpret_cast<const uint4*>(xq + k1);
+        const int rot = (c >> 1) & 3;                      // granule rotation of this 64-byte group (see the quantise prologue)
+        const int8_t* xg = xq + k0;
+        const uint4 x0 = *reinterpret_cast<const uint4*>(xg + ((rot & 3) << 4)), x1 = *reinterpret_cast<const uint4*>(xg + (((1 + rot) & 3) << 4));
+        const uint4 x2 = *reinterpret_cast<const uint4*>(xg + (((2 + rot) & 3) << 4)), x3 = *reinterpret_cast<const uint4*>(xg + (((3 + rot) & 3) << 4));
         const uint32_t qa[4] = {r.a.x, r.a.y, r.a.z, r.a.w}, qb[4] = {r.b.x, r.b.y, r.b.z, r.b.w};
-        const int isum = dp4a4(qa, xa) + dp4a4(qb, xb);
-        return us2f(r.d) * xd[k0 >> 5] * (float)isum;
+        const uint32_t qc[4] = {r.c.x, r.c.y, r.c.z, r.c.w}, qe[4] = {r.e.x, r.e.y, r.e.z, r.e.w};
+        const int i0 = dp4a4(qa, x0) + dp4a4(qb, x1), i1 = dp4a4(qc, x2) + dp4a4(qe, x3);
+        const float2 dd = h2_to_f2(r.d2);
+        return dd.x * xd[k0 >> 5] * (float)i0 + dd.y * xd[k1 >> 5] * (float)i1;
     } else if constexpr (WT == W_Q4_K || WT == W_Q5_K) {
         const int j = c & 3;
         const int rot = (c >> 1) & 3;                      // granule rotation of this 64-byte group (see the quantise prologue)
