@@ -166,14 +166,15 @@ class RpcEngine:
 
 
 def launch_local_workers(model: str, n_workers: int, base_port: int = 50052, n_ctx: int = 2048, n_layer: int | None = None,
-                         threads: int | None = None, verbose: bool = False) -> tuple[list[subprocess.Popen], list[str]]:
+                         threads: int | None = None, verbose: bool = False, sanitize: str | None = None,
+                         stderr=None) -> tuple[list[subprocess.Popen], list[str]]:
     """Start `n_workers` dlp-worker processes on localhost with an even layer split (the reference has no such script:
     `rpc-server` instances must be started by hand).  Returns (processes, endpoints)."""
     from ..gguf import open_gguf
     from ..models.config import config_from_gguf
     from ..runtime import native
     from .grid import stage_layer_ranges
-    native.build()
+    native.build(sanitize=sanitize)
     if n_layer is None:
         f = open_gguf(model)
         n_layer = config_from_gguf(f.metadata, f.tensors).n_layer
@@ -184,9 +185,9 @@ def launch_local_workers(model: str, n_workers: int, base_port: int = 50052, n_c
         env["OMP_NUM_THREADS"] = str(threads)
     for i, r in enumerate(stage_layer_ranges(n_layer, n_workers)):
         port = base_port + i
-        cmd = [native.path("dlp-worker"), "-m", model, "--layers", f"{r.start}:{r.stop}", "-p", str(port), "-c", str(n_ctx)]
+        cmd = [native.path("dlp-worker", sanitize), "-m", model, "--layers", f"{r.start}:{r.stop}", "-p", str(port), "-c", str(n_ctx)]
         if verbose:
             cmd.append("-v")
-        procs.append(subprocess.Popen(cmd, env=env))
+        procs.append(subprocess.Popen(cmd, env=env, stderr=stderr))
         eps.append(f"127.0.0.1:{port}")
     return procs, eps

@@ -12,23 +12,32 @@ TARGETS = {
 }
 
 
-def path(name: str) -> str:
-    return os.path.join(BIN, name)
+# Sanitizer builds (parity: the reference's LLAMA_SANITIZE_{ADDRESS,THREAD,UNDEFINED} CMake switches): the same
+# sources compiled with -fsanitize=... into bin/<kind>/; tests/test_sanitizers.py drives them with real traffic.
+SANITIZERS = {"address": ["-fsanitize=address,undefined", "-fno-omit-frame-pointer", "-g", "-O1"],
+              "thread": ["-fsanitize=thread", "-fno-omit-frame-pointer", "-g", "-O1"]}
 
 
-def build(force: bool = False) -> dict[str, str]:
-    os.makedirs(BIN, exist_ok=True)
+def path(name: str, sanitize: str | None = None) -> str:
+    return os.path.join(BIN, sanitize, name) if sanitize else os.path.join(BIN, name)
+
+
+def build(force: bool = False, sanitize: str | None = None) -> dict[str, str]:
+    if sanitize and sanitize not in SANITIZERS:
+        raise ValueError(f"unknown sanitizer {sanitize!r}; known: {sorted(SANITIZERS)}")
+    os.makedirs(os.path.join(BIN, sanitize) if sanitize else BIN, exist_ok=True)
     out = {}
     for name, (srcs, flags) in TARGETS.items():
         src_paths = [os.path.join(HERE, s) for s in srcs]
         if not all(os.path.exists(s) for s in src_paths):
             continue
-        dst = path(name)
+        dst = path(name, sanitize)
         deps = src_paths + [os.path.join(HERE, f) for f in os.listdir(HERE) if f.endswith(".h")]
         if not force and os.path.exists(dst) and all(os.path.getmtime(dst) >= os.path.getmtime(d) for d in deps):
             out[name] = dst
             continue
-        cmd = ["g++", "-O3", "-std=c++17", "-Wall", "-Wno-unused-function"] + flags + src_paths + ["-o", dst]
+        opt = SANITIZERS[sanitize] if sanitize else ["-O3"]
+        cmd = ["g++", "-std=c++17", "-Wall", "-Wno-unused-function"] + opt + flags + src_paths + ["-o", dst]
         res = subprocess.run(cmd, capture_output=True, text=True)
         if res.returncode != 0:
             raise RuntimeError(f"building {name} failed:\n{res.stderr}")

@@ -492,6 +492,7 @@ bool serve_client(int fd, Stage& st, bool verbose) {
         payload.resize(rq.nbytes);
         if (rq.nbytes && !recv_all(fd, payload.data(), rq.nbytes)) return true;
         if (!hello && rq.cmd != HELLO) { reply(fd, 3, "HELLO first", 11); return true; }   // same rule as the reference (ggml-rpc.cpp:1584)
+        const uint32_t seq_id = rq.seq;   // the wire struct is packed: never bind references to its (misaligned) members
         try {
             switch (rq.cmd) {
                 case HELLO: {
@@ -505,13 +506,13 @@ bool serve_client(int fd, Stage& st, bool verbose) {
                     break;
                 }
                 case RUN: {
-                    std::vector<float> out = st.run(rq.seq, (int)rq.n_tokens, (int)rq.pos0, rq.flags, payload.data(), payload.size());
-                    if (verbose) fprintf(stderr, "RPC worker[%d:%d) seq %u: %u tokens @%u -> %zu floats\n", st.l0, st.l1, rq.seq, rq.n_tokens, rq.pos0, out.size());
+                    std::vector<float> out = st.run(seq_id, (int)rq.n_tokens, (int)rq.pos0, rq.flags, payload.data(), payload.size());
+                    if (verbose) fprintf(stderr, "RPC worker[%d:%d) seq %u: %u tokens @%u -> %zu floats\n", st.l0, st.l1, seq_id, (unsigned)rq.n_tokens, (unsigned)rq.pos0, out.size());
                     if (!reply(fd, 0, out.data(), out.size() * 4)) return true;
                     break;
                 }
-                case RESET: st.seqs.erase(rq.seq); reply(fd, 0, nullptr, 0); break;
-                case TRUNCATE: { auto it = st.seqs.find(rq.seq); if (it != st.seqs.end()) it->second.len = std::min<int>(it->second.len, (int)rq.pos0); reply(fd, 0, nullptr, 0); break; }
+                case RESET: st.seqs.erase(seq_id); reply(fd, 0, nullptr, 0); break;
+                case TRUNCATE: { auto it = st.seqs.find(seq_id); if (it != st.seqs.end()) it->second.len = std::min<int>(it->second.len, (int)rq.pos0); reply(fd, 0, nullptr, 0); break; }
                 case SHUTDOWN: reply(fd, 0, nullptr, 0); return false;
                 default: reply(fd, 5, "unknown command", 15); return true;
             }
