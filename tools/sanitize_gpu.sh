@@ -1,5 +1,7 @@
 #!/usr/bin/env bash
 # compute-sanitizer over a subset of the kernel tests (the reference has no compute-sanitizer integration).
+# NOTE: on the development pool compute-sanitizer is disabled ("closed on this pool"): this script is for boxes where it is
+# available; in-tree the kernels are guarded by DLP_REQUIRE argument checks, small-shape tests and the CPU-oracle comparison.
 #   tools/sanitize_gpu.sh memcheck|racecheck|synccheck ["pytest -k expression"]
 TOOL=${1:-memcheck}
 EXPR=${2:-"onepass and 128-8-2 or gemv_store_and_add and 1- or rope_kv_write"}
