@@ -94,7 +94,16 @@ class _KvStub:
 class RpcEngine:
     """LlamaEngine-shaped facade over a chain of workers (stage i feeds stage i+1)."""
 
-    def __init__(self, endpoints: list[str], n_ctx: int | None = None, max_seqs: int = 4):
+    def __init__(self, endpoints: list[str], n_ctx: int | None = None, max_seqs: int = 4, recover: bool = False,
+                 recover_wait_s: float = 30.0):
+        """`recover=True`: when a worker dies mid-request (connection reset / closed) the engine waits up to `recover_wait_s`
+        for the endpoint to come back (a supervisor such as `LocalWorkerPool` restarts it), reconnects the whole chain, replays
+        the token history of every live sequence to rebuild the workers' KV caches and repeats the failed call - the caller
+        only sees a slower step.  The reference aborts the client process in this situation (`ggml-rpc.cpp:66`)."""
+        self.endpoints = list(endpoints)
+        self.recover, self.recover_wait_s = recover, recover_wait_s
+        self.history: dict[int, list[int]] = {}
+        self.n_recoveries = 0
         self.workers = []
         for ep in endpoints:
             host, _, port = ep.rpartition(":")
@@ -121,24 +130,69 @@ class RpcEngine:
     def alloc_seq(self) -> int:
         sid = self._free.pop()
         self.lens[sid] = 0
+        self.history[sid] = []
         return sid
 
     def free_seq(self, sid: int):
-        for w in self.workers:
-            w.reset(sid)
+        self._guard(lambda: [w.reset(sid) for w in self.workers], skip_sid=sid)
         del self.lens[sid]
+        self.history.pop(sid, None)
         self._free.append(sid)
+
+    # ---- failure handling ---------------------------------------------------------------------------------------
+    def _reconnect_and_replay(self, skip_sid: int | None = None):
+        deadline = time.time() + self.recover_wait_s
+        for w in self.workers:
+            try:
+                w.close()
+            except OSError:
+                pass
+        workers = []
+        for ep in self.endpoints:
+            host, _, port = ep.rpartition(":")
+            while True:
+                try:
+                    workers.append(WorkerClient(host or "127.0.0.1", int(port), connect_retries=5))
+                    break
+                except WorkerError:
+                    if time.time() > deadline:
+                        raise
+                    time.sleep(0.2)
+        self.workers = workers
+        self.n_recoveries += 1
+        for sid, hist in self.history.items():          # surviving workers still hold stale caches: reset everywhere, then replay
+            for w in self.workers:
+                w.reset(sid)
+            n = self.lens.get(sid, 0) if sid != skip_sid else 0
+            self.lens[sid] = 0
+            if n:
+                self._forward_once(sid, hist[:n])
+
+    def _guard(self, fn, skip_sid: int | None = None):
+        try:
+            return fn()
+        except WorkerError:
+            if not self.recover:
+                raise
+            self._reconnect_and_replay(skip_sid)
+            return fn()
 
     def seq_len(self, sid: int) -> int:
         return self.lens[sid]
 
     def truncate_seq(self, sid: int, new_len: int):
         new_len = max(0, min(new_len, self.lens[sid]))
-        for w in self.workers:
-            w.truncate(sid, new_len)
-        self.lens[sid] = new_len
+        self.lens[sid] = new_len                          # (set first: a recovery replays exactly the kept prefix)
+        del self.history[sid][new_len:]
+        self._guard(lambda: [w.truncate(sid, new_len) for w in self.workers])
 
     def _forward(self, sid: int, tokens, all_logits=False) -> torch.Tensor:
+        toks = [int(t) for t in np.asarray(tokens, dtype=np.int32).reshape(-1)]
+        out = self._guard(lambda: self._forward_once(sid, toks, all_logits))
+        self.history[sid][self.lens[sid] - len(toks):] = toks
+        return out
+
+    def _forward_once(self, sid: int, tokens, all_logits=False) -> torch.Tensor:
         toks = np.asarray(tokens, dtype=np.int32).reshape(-1)
         T, pos0 = toks.size, self.lens[sid]
         data = toks.tobytes()
@@ -191,3 +245,52 @@ def launch_local_workers(model: str, n_workers: int, base_port: int = 50052, n_c
         procs.append(subprocess.Popen(cmd, env=env, stderr=stderr))
         eps.append(f"127.0.0.1:{port}")
     return procs, eps
+
+
+class LocalWorkerPool:
+    """Supervised local workers ("auto-heal", proposed but not implemented in the reference's design report, PDF p.7): a monitor
+    thread restarts any dlp-worker that exits, with the same layer range and port, so that `RpcEngine(recover=True)` can
+    reconnect and replay."""
+
+    def __init__(self, model: str, n_workers: int, base_port: int = 50052, n_ctx: int = 2048, threads: int | None = None):
+        import threading
+        from ..gguf import open_gguf
+        from ..models.config import config_from_gguf
+        from ..runtime import native
+        from .grid import stage_layer_ranges
+        native.build()
+        f = open_gguf(model)
+        n_layer = config_from_gguf(f.metadata, f.tensors).n_layer
+        f.close()
+        self.env = dict(os.environ)
+        if threads:
+            self.env["OMP_NUM_THREADS"] = str(threads)
+        self.cmds, self.endpoints = [], []
+        for i, r in enumerate(stage_layer_ranges(n_layer, n_workers)):
+            self.cmds.append([native.path("dlp-worker"), "-m", model, "--layers", f"{r.start}:{r.stop}", "-p", str(base_port + i), "-c", str(n_ctx)])
+            self.endpoints.append(f"127.0.0.1:{base_port + i}")
+        self.procs = [subprocess.Popen(c, env=self.env) for c in self.cmds]
+        self.restarts = 0
+        self._stop = False
+        self._thread = threading.Thread(target=self._monitor, daemon=True)
+        self._thread.start()
+
+    def _monitor(self):
+        while not self._stop:
+            for i, p in enumerate(self.procs):
+                if p.poll() is not None and not self._stop:
+                    self.procs[i] = subprocess.Popen(self.cmds[i], env=self.env)
+                    self.restarts += 1
+            time.sleep(0.1)
+
+    def stop(self):
+        self._stop = True
+        self._thread.join(timeout=2)
+        for p in self.procs:
+            if p.poll() is None:
+                p.terminate()
+        for p in self.procs:
+            try:
+                p.wait(timeout=10)
+            except subprocess.TimeoutExpired:
+                p.kill()

@@ -74,3 +74,41 @@ def test_worker_validates_requests(chain):
     with pytest.raises(WorkerError, match="out of range"):
         w.run(7, 1, 0, (10 ** 6).to_bytes(4, "little"))     # token id beyond the vocabulary
     w.reset(7)
+
+
+def test_worker_crash_is_healed_by_reconnect_and_replay(tmp_models):
+    """Fault injection: SIGKILL one stage worker in the middle of a generation.  The pool restarts it, the engine reconnects,
+    replays the sequence history into the fresh KV caches and the token stream is identical to an undisturbed run."""
+    import os
+    import signal
+    from distributed_llm_pipeline_b200.parallel.rpc import LocalWorkerPool
+    path = tmp_models[("tiny", "Q8_0")]
+    pool = LocalWorkerPool(path, 2, base_port=_free_ports(1)[0], n_ctx=128, threads=2)
+    try:
+        eng = RpcEngine(pool.endpoints, max_seqs=2, recover=True, recover_wait_s=30)
+        prompt = [1, 5, 9, 200, 33, 7, 8]
+
+        def run(kill_at):
+            sid = eng.alloc_seq()
+            logits = eng.prefill(sid, prompt)
+            out = [int(logits.argmax())]
+            for i in range(10):
+                if i == kill_at:
+                    os.kill(pool.procs[1].pid, signal.SIGKILL)
+                out.append(int(eng.decode([sid], [out[-1]], sample=False)[0].argmax()))
+            eng.free_seq(sid)
+            return out
+        clean = run(-1)
+        healed = run(4)
+        assert healed == clean
+        assert eng.n_recoveries >= 1 and pool.restarts >= 1
+        eng.close()                                                         # (a worker serves one client at a time)
+        plain = RpcEngine(pool.endpoints, max_seqs=1)                       # without recover=True the failure is a clean error
+        sid = plain.alloc_seq()
+        plain.prefill(sid, prompt)
+        os.kill(pool.procs[0].pid, signal.SIGKILL)
+        with pytest.raises(WorkerError):
+            for _ in range(3):
+                plain.decode([sid], [5], sample=False)
+    finally:
+        pool.stop()
