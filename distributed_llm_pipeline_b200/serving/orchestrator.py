@@ -144,7 +144,7 @@ class Orchestrator:
                                                        ("content-length", "0")]))
             await writer.drain()
             return True
-        is_api = method == "POST" or path in ("/metrics", "/slots", "/props", "/v1/models") or path.startswith("/slots/")
+        is_api = method == "POST" or path in ("/metrics", "/slots", "/props", "/v1/models", "/api/tags") or path.startswith("/slots/")
         if self.api_key and is_api and path != "/health":
             auth = headers.get("authorization", "")
             if auth != f"Bearer {self.api_key}" and headers.get("x-api-key", "") != self.api_key:
@@ -177,6 +177,14 @@ class Orchestrator:
                 return await self.completion(json.loads(body or b"{}"), writer, openai=path.startswith("/v1"))
             if method == "POST" and path == "/v1/chat/completions":
                 return await self.chat_completions(json.loads(body or b"{}"), writer)
+            if method == "POST" and path in ("/api/generate", "/api/chat"):
+                return await self.ollama(path, json.loads(body or b"{}"), writer)
+            if method == "GET" and path == "/api/tags":
+                await self._json(writer, {"models": [{"name": self.info.get("name", "model"), "model": self.info.get("name", "model"),
+                                                      "details": {"format": "gguf", "family": self.info.get("arch", "llama")}}]})
+                return True
+            if method == "POST" and path == "/v1/messages":
+                return await self.anthropic_messages(json.loads(body or b"{}"), writer)
             if method == "POST" and path == "/tokenize":
                 d = json.loads(body or b"{}")
                 await self._json(writer, {"tokens": self.sched.tok.encode(d.get("content", ""), add_bos=bool(d.get("add_special", False)))})
@@ -424,6 +432,83 @@ class Orchestrator:
                                   "choices": [{"index": 0, "message": {"role": "assistant", "content": req.text}, "finish_reason": req.finish_reason}],
                                   "usage": {"prompt_tokens": len(req.prompt_ids), "completion_tokens": len(req.output_ids),
                                             "total_tokens": len(req.prompt_ids) + len(req.output_ids)}, "timings": req.timings()})
+        return True
+
+    # ---- Ollama- and Anthropic-style routes (the reference server speaks both dialects, server.cpp:164-197) ------------
+    async def ollama(self, path: str, d: dict, writer) -> bool:
+        chat = path == "/api/chat"
+        prompt = apply_chat_template(self.info.get("metadata", {}), d.get("messages", [])) if chat else str(d.get("prompt", ""))
+        opts = dict(d.get("options") or {})
+        opts.setdefault("temperature", 0.8)
+        n_predict = int(opts.get("num_predict", self.n_predict))
+        stop = opts.get("stop") or []
+        req = Request(prompt=prompt, n_predict=n_predict if n_predict > 0 else self.sched.eng.n_ctx, sampling=self._sampling_from(opts),
+                      stop=[stop] if isinstance(stop, str) else list(stop))
+        model = str(d.get("model") or self.info.get("name", "model"))
+
+        def obj(text, done, reason=None):
+            o = {"model": model, "created_at": time.strftime("%Y-%m-%dT%H:%M:%SZ", time.gmtime()), "done": done}
+            if chat:
+                o["message"] = {"role": "assistant", "content": text}
+            else:
+                o["response"] = text
+            if done:
+                o.update(done_reason=reason, prompt_eval_count=len(req.prompt_ids), eval_count=len(req.output_ids))
+            return o
+        if d.get("stream", True):                    # Ollama streams newline-delimited JSON by default
+            writer.write(self._head("200 OK", [("content-type", "application/x-ndjson")] + CORS + [("connection", "close")]))
+
+            def fmt(kind, content):
+                if kind == "token":
+                    return json.dumps(obj(content, False)).encode() + b"\n"
+                if kind == "done":
+                    return json.dumps(obj("", True, content)).encode() + b"\n"
+                return None
+            await self._stream_request(req, writer, fmt)
+            return False
+        await self._run_blocking(req)
+        await self._json(writer, obj(req.text, True, req.finish_reason))
+        return True
+
+    async def anthropic_messages(self, d: dict, writer) -> bool:
+        msgs = list(d.get("messages", []))
+        norm = []
+        if d.get("system"):
+            sys_txt = d["system"] if isinstance(d["system"], str) else "".join(b.get("text", "") for b in d["system"])
+            norm.append({"role": "system", "content": sys_txt})
+        for m in msgs:
+            c = m.get("content", "")
+            norm.append({"role": m.get("role", "user"), "content": c if isinstance(c, str) else "".join(b.get("text", "") for b in c)})
+        stop = d.get("stop_sequences") or []
+        req = Request(prompt=apply_chat_template(self.info.get("metadata", {}), norm), n_predict=int(d.get("max_tokens", self.n_predict)),
+                      sampling=self._sampling_from(d), stop=list(stop))
+        rid = "msg_" + uuid.uuid4().hex[:24]
+        model = str(d.get("model") or self.info.get("name", "model"))
+        if d.get("stream"):
+            writer.write(self._head("200 OK", [("content-type", "text/event-stream"), ("cache-control", "no-cache")] + CORS + [("connection", "close")]))
+
+            def ev(name, o):
+                return f"event: {name}\ndata: {json.dumps(o)}\n\n".encode()
+            writer.write(ev("message_start", {"type": "message_start", "message": {"id": rid, "type": "message", "role": "assistant", "model": model,
+                                                                                   "content": [], "stop_reason": None}}))
+            writer.write(ev("content_block_start", {"type": "content_block_start", "index": 0, "content_block": {"type": "text", "text": ""}}))
+
+            def fmt(kind, content):
+                if kind == "token":
+                    return ev("content_block_delta", {"type": "content_block_delta", "index": 0, "delta": {"type": "text_delta", "text": content}})
+                if kind == "done":
+                    reason = "max_tokens" if content == "length" else "end_turn"
+                    return (ev("content_block_stop", {"type": "content_block_stop", "index": 0}) +
+                            ev("message_delta", {"type": "message_delta", "delta": {"stop_reason": reason}, "usage": {"output_tokens": len(req.output_ids)}}) +
+                            ev("message_stop", {"type": "message_stop"}))
+                return None
+            await self._stream_request(req, writer, fmt)
+            return False
+        await self._run_blocking(req)
+        await self._json(writer, {"id": rid, "type": "message", "role": "assistant", "model": model,
+                                  "content": [{"type": "text", "text": req.text}],
+                                  "stop_reason": "max_tokens" if req.finish_reason == "length" else "end_turn", "stop_sequence": None,
+                                  "usage": {"input_tokens": len(req.prompt_ids), "output_tokens": len(req.output_ids)}})
         return True
 
     async def _run_blocking(self, req: Request):

@@ -283,3 +283,24 @@ def test_model_router_loads_on_demand_and_unloads_lru(tmp_models):
             break
         time.sleep(0.3)
     assert json.loads(body)["models_loaded"] == []
+
+
+def test_ollama_and_anthropic_dialects(server):
+    port, _ = server
+    _, _, body = _http(port, "POST", "/api/generate", json.dumps({"prompt": "a b c", "stream": False, "options": {"num_predict": 4, "temperature": 0}}).encode())
+    d = json.loads(body)
+    assert d["done"] is True and isinstance(d["response"], str) and d["eval_count"] <= 4
+    _, hdr, body = _http(port, "POST", "/api/chat", json.dumps({"messages": [{"role": "user", "content": "hi"}], "options": {"num_predict": 3, "temperature": 0}}).encode())
+    lines = [json.loads(l) for l in body.decode().splitlines() if l.strip()]          # default: NDJSON stream
+    assert lines[-1]["done"] is True and all("message" in l for l in lines)
+    _, _, body = _http(port, "GET", "/api/tags")
+    assert json.loads(body)["models"]
+    _, _, body = _http(port, "POST", "/v1/messages", json.dumps({"system": "be brief", "max_tokens": 4, "temperature": 0,
+                                                                   "messages": [{"role": "user", "content": [{"type": "text", "text": "hello"}]}]}).encode())
+    d = json.loads(body)
+    assert d["type"] == "message" and d["content"][0]["type"] == "text" and d["usage"]["output_tokens"] <= 4
+    assert d["stop_reason"] in ("max_tokens", "end_turn")
+    _, _, body = _http(port, "POST", "/v1/messages", json.dumps({"max_tokens": 3, "temperature": 0, "stream": True,
+                                                                   "messages": [{"role": "user", "content": "hello"}]}).encode())
+    text = body.decode()
+    assert "event: message_start" in text and "event: content_block_delta" in text and text.rstrip().endswith('{"type": "message_stop"}')
