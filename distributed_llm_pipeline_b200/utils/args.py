@@ -40,6 +40,8 @@ COMMON = [
     Opt(("-fa", "--flash-attn"), "accepted for compatibility: attention is always flash", "on", str, "DLP_ARG_FLASH_ATTN"),
     Opt(("--lora",), "comma separated LoRA adapter GGUFs, each optionally path:scale (merged at load)", None, str, "DLP_ARG_LORA"),
     Opt(("--device",), "cuda | cpu", "cuda", str, "DLP_ARG_DEVICE"),
+    Opt(("--list-devices",), "print the available devices and exit", False, None, action="store_true"),
+    Opt(("--fit",), "shrink -c / -np until weights + KV cache fit the device memory", False, None, "DLP_ARG_FIT", action="store_true"),
     Opt(("-v", "--verbose"), "debug logging", False, None, "DLP_ARG_VERBOSE", action="store_true"),
     Opt(("--log-file",), "also write logs to this file", None, str, "DLP_ARG_LOG_FILE"),
     Opt(("--trace",), "write a chrome://tracing JSON of the run", None, str, "DLP_ARG_TRACE"),

@@ -55,3 +55,21 @@ def test_tokenize_perplexity_bench_cli(tmp_models):
     assert '"test": "pp16"' in out and '"test": "tg4"' in out
     out = _run("dlp_cli.py", "-m", model, "--device", "cpu", "-p", "hi", "-n", "4", "-st", "--temp", "0")
     assert len(out) > 0
+
+
+def test_fit_params_and_list_devices(tmp_models):
+    from distributed_llm_pipeline_b200.models.config import config_from_gguf
+    from distributed_llm_pipeline_b200.utils.fit import fit_params, list_devices, model_bytes
+    f = open_gguf(tmp_models[("tiny", "F16")])
+    cfg = config_from_gguf(f.metadata, f.tensors)
+    mb = model_bytes(f)
+    kv_tok = 2 * cfg.n_layer * cfg.kv_dim * 2
+    big = fit_params(f, cfg, 512, 4, 10 << 30)
+    assert big.fits and (big.n_ctx, big.n_slots) == (512, 4)
+    tight = fit_params(f, cfg, 4096, 4, int((mb + (64 << 20) + kv_tok * 1024) / 0.92))
+    assert tight.fits and tight.n_ctx * tight.n_slots * kv_tok <= kv_tok * 1100 and tight.n_ctx % 64 == 0 and tight.n_slots >= 1
+    none = fit_params(f, cfg, 512, 1, mb // 2)
+    assert not none.fits and none.min_tp >= 2 and "--tp" in none.note
+    assert any(d.startswith("CPU") for d in list_devices())
+    out = _run("dlp_cli.py", "--list-devices")
+    assert "Available devices" in out

@@ -17,6 +17,10 @@ from distributed_llm_pipeline_b200.utils.log import get_logger  # noqa: E402
 
 def main(argv=None):
     a = build_parser("dlp-cli - generate text from a GGUF model", [COMMON, SAMPLING, GENERATION, SPECULATIVE]).parse_args(argv)
+    if a.list_devices:
+        from distributed_llm_pipeline_b200.utils.fit import list_devices
+        print("Available devices:\n  " + "\n  ".join(list_devices()))
+        return
     if not a.model:
         sys.exit("dlp-cli: -m model.gguf is required")
     log = get_logger()
@@ -40,6 +44,14 @@ def main(argv=None):
         from distributed_llm_pipeline_b200.models.weights import load_weights
         dev = a.device if (a.device != "cuda" or torch.cuda.is_available()) else "cpu"
         f = open_gguf(a.model)
+        if a.fit and dev != "cpu":
+            from distributed_llm_pipeline_b200.models.config import config_from_gguf
+            from distributed_llm_pipeline_b200.utils.fit import fit_params
+            fr = fit_params(f, config_from_gguf(f.metadata, f.tensors), a.ctx_size, a.parallel, torch.cuda.mem_get_info()[0])
+            log.info(f"fit: {fr.note}")
+            if not fr.fits:
+                sys.exit(f"dlp-cli: {fr.note}")
+            a.ctx_size, a.parallel = fr.n_ctx, fr.n_slots
         w = load_weights(f, dev, lora=lora_from_args(a))
         eng = LlamaEngine(w, n_ctx=a.ctx_size, max_seqs=a.parallel, page_size=64 if dev != "cpu" else 16,
                           max_batch_tokens=min(a.batch_size, a.ubatch_size))
