@@ -51,6 +51,16 @@ struct Tensor {
     uint64_t cols() const { return ne.empty() ? 0 : ne[0]; }
 };
 
+size_t row_bytes(uint32_t type, uint64_t k);
+// rows [r0, r1) of a 2-D tensor as a tensor of its own (phi3 keeps Q|K|V and gate|up in one matrix each)
+Tensor slice_rows(const Tensor& t, uint64_t r0, uint64_t r1) {
+    Tensor v;
+    v.ne = {t.cols(), r1 - r0};
+    v.type = t.type;
+    v.data = t.data + r0 * row_bytes(t.type, t.cols());
+    return v;
+}
+
 size_t row_bytes(uint32_t type, uint64_t k) {
     switch (type) {
         case T_F32: return k * 4;
@@ -346,7 +356,8 @@ void rmsnorm(const float* x, const float* w, float eps, int T, int E, float* out
 }
 
 // ---- model stage ------------------------------------------------------------------------------------------------------
-struct Hparams { int n_embd, n_layer, n_head, n_head_kv, head_dim, n_ff, n_vocab, n_rot, n_ctx; float eps, theta; };
+struct Hparams { int n_embd, n_layer, n_head, n_head_kv, head_dim, n_ff, n_vocab, n_rot, n_ctx; float eps, theta;
+                 bool neox = false, qkv_bias = false, qk_norm = false, fused_qkv = false; };
 
 struct SeqCache { std::vector<std::vector<float>> k, v; int len = 0; };  // per local layer: [n_ctx][Hkv*D]
 
@@ -361,7 +372,12 @@ struct Stage {
     void load(const std::string& path, int a, int b, int n_ctx) {
         g.open(path);
         const std::string ar = g.str.count("general.architecture") ? g.str["general.architecture"] : "llama";
-        if (ar != "llama") throw std::runtime_error("the CPU worker runs llama-architecture checkpoints only (got " + ar + "); use the GPU engine");
+        if (ar != "llama" && ar != "qwen2" && ar != "qwen3" && ar != "phi3")
+            throw std::runtime_error("the CPU worker runs llama / qwen2 / qwen3 / phi3 checkpoints (got " + ar + ")");
+        hp.neox = ar != "llama";                                   // half-split rotation for the other families
+        hp.qkv_bias = g.has("blk.0.attn_q.bias");                  // qwen2
+        hp.qk_norm = g.has("blk.0.attn_q_norm.weight");            // qwen3
+        hp.fused_qkv = g.has("blk.0.attn_qkv.weight");             // phi3
         auto N = [&](const char* k, double d) { return g.n(ar + "." + k, d); };
         hp.n_embd = (int)N("embedding_length", 0); hp.n_layer = (int)N("block_count", 0);
         hp.n_head = (int)N("attention.head_count", 0); hp.n_head_kv = (int)N("attention.head_count_kv", hp.n_head);
@@ -394,9 +410,10 @@ struct Stage {
         for (int h = 0; h < n_heads; ++h)
             for (int i = 0; i < hp.n_rot / 2; ++i) {
                 const float a = pos * inv_freq[i], c = std::cos(a), s = std::sin(a);
-                float* p = x + (size_t)h * D + 2 * i;
-                const float x0 = p[0], x1 = p[1];
-                p[0] = x0 * c - x1 * s; p[1] = x0 * s + x1 * c;
+                float* p0 = x + (size_t)h * D + (hp.neox ? i : 2 * i);
+                float* p1 = hp.neox ? p0 + hp.n_rot / 2 : p0 + 1;
+                const float x0 = *p0, x1 = *p1;
+                *p0 = x0 * c - x1 * s; *p1 = x0 * s + x1 * c;
             }
     }
 
@@ -428,9 +445,34 @@ struct Stage {
         for (int il = l0; il < l1; ++il) {
             const std::string p = "blk." + std::to_string(il) + ".";
             rmsnorm(h.data(), (const float*)g.get(p + "attn_norm.weight").data, hp.eps, T, E, xn.data());
-            matmul(g.get(p + "attn_q.weight"), xn.data(), T, q.data());
-            matmul(g.get(p + "attn_k.weight"), xn.data(), T, k.data());
-            matmul(g.get(p + "attn_v.weight"), xn.data(), T, v.data());
+            if (hp.fused_qkv) {
+                const Tensor& w = g.get(p + "attn_qkv.weight");
+                matmul(slice_rows(w, 0, qd), xn.data(), T, q.data());
+                matmul(slice_rows(w, qd, qd + kvd), xn.data(), T, k.data());
+                matmul(slice_rows(w, qd + kvd, qd + 2 * kvd), xn.data(), T, v.data());
+            } else {
+                matmul(g.get(p + "attn_q.weight"), xn.data(), T, q.data());
+                matmul(g.get(p + "attn_k.weight"), xn.data(), T, k.data());
+                matmul(g.get(p + "attn_v.weight"), xn.data(), T, v.data());
+            }
+            if (hp.qkv_bias) {
+                const float* bq = (const float*)g.get(p + "attn_q.bias").data;
+                const float* bk = (const float*)g.get(p + "attn_k.bias").data;
+                const float* bv = (const float*)g.get(p + "attn_v.bias").data;
+                for (int t = 0; t < T; ++t) {
+                    for (int i = 0; i < qd; ++i) q[(size_t)t * qd + i] += bq[i];
+                    for (int i = 0; i < kvd; ++i) { k[(size_t)t * kvd + i] += bk[i]; v[(size_t)t * kvd + i] += bv[i]; }
+                }
+            }
+            if (hp.qk_norm) {   // per-head RMSNorm over head_dim, before the rotation
+                std::vector<float> tmp(std::max(qd, kvd));
+                for (int t = 0; t < T; ++t) {
+                    rmsnorm(q.data() + (size_t)t * qd, (const float*)g.get(p + "attn_q_norm.weight").data, hp.eps, Hq, D, tmp.data());
+                    memcpy(q.data() + (size_t)t * qd, tmp.data(), (size_t)qd * 4);
+                    rmsnorm(k.data() + (size_t)t * kvd, (const float*)g.get(p + "attn_k_norm.weight").data, hp.eps, Hkv, D, tmp.data());
+                    memcpy(k.data() + (size_t)t * kvd, tmp.data(), (size_t)kvd * 4);
+                }
+            }
             std::vector<float>& kc = c.k[il - l0];
             std::vector<float>& vc = c.v[il - l0];
             for (int t = 0; t < T; ++t) {
@@ -455,8 +497,14 @@ struct Stage {
                 }
             matmul(g.get(p + "attn_output.weight"), att.data(), T, h.data(), true);
             rmsnorm(h.data(), (const float*)g.get(p + "ffn_norm.weight").data, hp.eps, T, E, xn.data());
-            matmul(g.get(p + "ffn_gate.weight"), xn.data(), T, gate.data());
-            matmul(g.get(p + "ffn_up.weight"), xn.data(), T, up.data());
+            if (hp.fused_qkv) {   // phi3: ffn_up = [gate | up]
+                const Tensor& w = g.get(p + "ffn_up.weight");
+                matmul(slice_rows(w, 0, F), xn.data(), T, gate.data());
+                matmul(slice_rows(w, F, 2 * (uint64_t)F), xn.data(), T, up.data());
+            } else {
+                matmul(g.get(p + "ffn_gate.weight"), xn.data(), T, gate.data());
+                matmul(g.get(p + "ffn_up.weight"), xn.data(), T, up.data());
+            }
             for (size_t i = 0; i < (size_t)T * F; ++i) gate[i] = gate[i] / (1.0f + std::exp(-gate[i])) * up[i];
             matmul(g.get(p + "ffn_down.weight"), gate.data(), T, h.data(), true);
         }

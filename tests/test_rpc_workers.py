@@ -112,3 +112,28 @@ def test_worker_crash_is_healed_by_reconnect_and_replay(tmp_models):
                 plain.decode([sid], [5], sample=False)
     finally:
         pool.stop()
+
+
+@pytest.mark.parametrize("key", [("tiny-qwen2", "Q8_0"), ("tiny-qwen3", "F16"), ("tiny-phi3", "Q8_0")])
+def test_other_architectures_on_cpu_workers(tmp_models, key):
+    """qwen2 (bias), qwen3 (per-head Q/K norm), phi3 (fused tensors), all half-split RoPE, through two native stage workers."""
+    path = tmp_models[key]
+    procs, eps = launch_local_workers(path, 2, base_port=_free_ports(1)[0], n_ctx=64, threads=2)
+    try:
+        eng = RpcEngine(eps, max_seqs=1)
+        ref = ReferenceModel.from_gguf(path)
+        prompt = [1, 5, 9, 200, 33, 7, 8, 100, 42]
+        toks, ref_logits = ref.generate_greedy(prompt, 3)
+        sid = eng.alloc_seq()
+        tol = 3e-4 if key[1] == "Q8_0" else 1e-6
+        assert nmse(ref_logits[0], eng.prefill(sid, prompt)) < tol
+        for i, t in enumerate(toks[:-1]):
+            assert nmse(ref_logits[i + 1], eng.decode([sid], [t], sample=False)[0]) < tol
+        for w in eng.workers:
+            w.shutdown()
+    finally:
+        for p in procs:
+            try:
+                p.wait(timeout=10)
+            except Exception:
+                p.kill()
