@@ -1,4 +1,5 @@
 #!/usr/bin/env bash
+# full GPU suite + attention-variant sweep + default bench (one gpurun call)
 mkdir -p gpurun_out
 timeout 900 python -m pytest tests -m gpu -x -q 2>&1 | tail -4
 timeout 600 python tools/ab_onepass.py 2>&1 | grep ctx
