@@ -489,11 +489,8 @@ template <int D, int G>
 static int launch_attn_rope_g(const AttnParams& p, const float* qkv, const float* inv_freq, const float2* rope_cs, __half* kc_w,
                               __half* vc_w, int neox, float q_scale, cudaStream_t s) {
     auto kern = attn_decode_rope_kernel<D, G>;
-    static bool opted_in = false;          // cluster sizes above 8 are "non-portable": opt in once per kernel instance
-    if (p.n_splits > 8 && !opted_in) {
+    if (first_use_on_device((const void*)kern))   // cluster sizes above 8 are "non-portable": opt in once per device
         DLP_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeNonPortableClusterSizeAllowed, 1));
-        opted_in = true;
-    }
     const int gqa = p.Hq / p.Hkv;
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3(p.n_splits, p.Hkv * (gqa / G), p.nq);
@@ -768,13 +765,13 @@ int attn_prefill(const __half* q, const __half* kc, const __half* vc, const int*
     dim3 grid((T + 63) / 64, Hq);
     if (D == 128) {
         const int smem = 5 * 64 * (128 + 8) * 2;   // Q + 2 stages x (K, V)
-        static bool cfg = false;
-        if (!cfg) { DLP_CHECK_CUDA(cudaFuncSetAttribute(attn_prefill_kernel<128>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem)); cfg = true; }
+        if (first_use_on_device((const void*)attn_prefill_kernel<128>))
+            DLP_CHECK_CUDA(cudaFuncSetAttribute(attn_prefill_kernel<128>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
         attn_prefill_kernel<128><<<grid, 128, smem, s>>>(q, kc, vc, bt_row, out, T, pos0, Hq, Hkv, page_size);
     } else if (D == 64) {
         const int smem = 5 * 64 * (64 + 8) * 2;
-        static bool cfg64 = false;
-        if (!cfg64) { DLP_CHECK_CUDA(cudaFuncSetAttribute(attn_prefill_kernel<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem)); cfg64 = true; }
+        if (first_use_on_device((const void*)attn_prefill_kernel<64>))
+            DLP_CHECK_CUDA(cudaFuncSetAttribute(attn_prefill_kernel<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
         attn_prefill_kernel<64><<<grid, 128, smem, s>>>(q, kc, vc, bt_row, out, T, pos0, Hq, Hkv, page_size);
     } else {
         DLP_REQUIRE(false, "attn_prefill: head dim %d unsupported (64, 128)", D);

@@ -5,6 +5,9 @@
 
 #include "../include/dlp_b200.h"
 #include "kernels.cuh"
+#include <mutex>
+#include <set>
+#include <utility>
 
 namespace dlp {
 
@@ -27,6 +30,14 @@ bool pdl_enabled() {
     return g_pdl != 0;
 }
 void set_pdl(bool on) { g_pdl = on ? 1 : 0; }
+bool first_use_on_device(const void* kernel) {
+    static std::mutex mu;
+    static std::set<std::pair<int, const void*>> seen;
+    int dev = 0;
+    cudaGetDevice(&dev);
+    std::lock_guard<std::mutex> lock(mu);
+    return seen.insert({dev, kernel}).second;
+}
 static unsigned long long* g_trace = nullptr;
 unsigned long long* trace_buffer() { return g_trace; }
 void set_trace_buffer(unsigned long long* buf) { g_trace = buf; }

@@ -50,6 +50,8 @@ int sm_count();  // cached multiprocessor count of the current device
 unsigned long long* trace_buffer();
 void set_trace_buffer(unsigned long long* buf);
 enum TraceId : unsigned { TR_BEGIN = 0, TR_WAITED = 1, TR_MAIN_DONE = 2, TR_END = 3, TR_GEMV = 1 << 8, TR_ROPE = 2 << 8, TR_ATTN = 3 << 8 };
+// One-time per-(device, kernel) configuration (cudaFuncSetAttribute is a per-device setting): true exactly once per pair.
+bool first_use_on_device(const void* kernel);
 bool pdl_enabled();  // programmatic dependent launch between consecutive kernels (env DLP_PDL=0 disables)
 void set_pdl(bool on);
 

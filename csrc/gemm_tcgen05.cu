@@ -355,11 +355,8 @@ static int launch_gemm(const CUtensorMap& tw0, const CUtensorMap& tw1, const CUt
                        int splits, cudaStream_t stream, const QWeight& qw0 = QWeight(), const QWeight& qw1 = QWeight()) {
     using Cfg = GemmCfg<BT, NA>;
     auto kern = gemm_tcgen05_kernel<BT, NA, AB_FMT, WT>;
-    static bool configured = false;
-    if (!configured) {
+    if (first_use_on_device((const void*)kern))
         DLP_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES));
-        configured = true;
-    }
     dim3 grid((p.N + GEMM_BM - 1) / GEMM_BM, (p.T + BT - 1) / BT, splits);
     kern<<<grid, 192, Cfg::SMEM_BYTES, stream>>>(tw0, tw1, tx, p, qw0, qw1);
     DLP_LAUNCH_CHECK();

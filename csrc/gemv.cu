@@ -388,14 +388,8 @@ __global__ void __launch_bounds__(256, 2) gemv_dense_v3_kernel(const GemvParams 
 
 template <typename Kern>
 static int launch_gemv_v3(Kern kern, const GemvParams& p, int U, size_t x_smem, cudaStream_t stream) {
-    static thread_local const void* configured[32];
-    static thread_local int n_configured = 0;
-    bool seen = false;
-    for (int i = 0; i < n_configured; ++i) seen |= configured[i] == (const void*)kern;
-    if (!seen) {
+    if (first_use_on_device((const void*)kern))
         DLP_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
-        if (n_configured < 32) configured[n_configured++] = (const void*)kern;
-    }
     const bool dual = p.out_mode == GV_SWIGLU_F16;
     const int rpu = dual ? 1 : 2;
     const int groups = (p.w0.N + rpu - 1) / rpu;
@@ -573,14 +567,8 @@ static bool bulk_config(const GemvParams& p, int T, size_t fixed_smem, BulkCfg& 
 
 template <typename Kern>
 static int launch_gemv_bulk(Kern kern, const GemvParams& p, const BulkCfg& cfg, size_t smem, cudaStream_t stream) {
-    static thread_local const void* configured[16];
-    static thread_local int n_configured = 0;
-    bool seen = false;
-    for (int i = 0; i < n_configured; ++i) seen |= configured[i] == (const void*)kern;
-    if (!seen) {
+    if (first_use_on_device((const void*)kern))
         DLP_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 216 * 1024));
-        if (n_configured < 16) configured[n_configured++] = (const void*)kern;
-    }
     int blocks = sm_count();
     if (blocks > cfg.n_groups) blocks = cfg.n_groups;
     DLP_CHECK_CUDA(launch_pdl(kern, dim3(blocks), dim3(288), smem, stream, p, cfg));
@@ -969,14 +957,8 @@ __global__ void __launch_bounds__(256, 2) gemv_quant_v3_kernel(const GemvParams 
 
 template <typename Kern>
 static int launch_gemv_qv3(Kern kern, const GemvParams& p, size_t x_smem, cudaStream_t stream, int chunk_w = 32) {
-    static thread_local const void* configured[32];
-    static thread_local int n_configured = 0;
-    bool seen = false;
-    for (int i = 0; i < n_configured; ++i) seen |= configured[i] == (const void*)kern;
-    if (!seen) {
+    if (first_use_on_device((const void*)kern))
         DLP_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
-        if (n_configured < 32) configured[n_configured++] = (const void*)kern;
-    }
     const bool dual = p.out_mode == GV_SWIGLU_F16;
     const int rpu = dual ? 1 : 2;
     const int groups = (p.w0.N + rpu - 1) / rpu;
@@ -1029,14 +1011,8 @@ int moe_route(const float* logits, int T, int n_expert, int top_k, int* ids, flo
 // ---------------------------------------------------------------------------------------------
 template <typename Kern>
 static int launch_gemv(Kern kern, const GemvParams& p, size_t smem, cudaStream_t stream) {
-    static thread_local const void* configured[64];
-    static thread_local int n_configured = 0;
-    bool seen = false;
-    for (int i = 0; i < n_configured; ++i) seen |= configured[i] == (const void*)kern;
-    if (!seen) {
+    if (first_use_on_device((const void*)kern))
         DLP_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
-        if (n_configured < 64) configured[n_configured++] = (const void*)kern;
-    }
     const bool dual = p.out_mode == GV_SWIGLU_F16;
     const int rows_per_block = 8 * (dual ? 1 : 2);
     int blocks = (p.w0.N + rows_per_block - 1) / rows_per_block;
