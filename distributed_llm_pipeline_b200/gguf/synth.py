@@ -181,6 +181,8 @@ def write_synthetic_gguf(path: str, cfg: ModelConfig, ftype: str = "F16", seed: 
         w.add(f"{a}.rope.scaling.type", "linear")
         w.add(f"{a}.rope.scaling.factor", float(1.0 / cfg.rope_scale_linear), ValueType.FLOAT32)
     if cfg.is_moe:
+        if a != "llama":
+            w.add(f"{a}.expert_feed_forward_length", cfg.n_ff, ValueType.UINT32)
         w.add(f"{a}.expert_count", cfg.n_expert, ValueType.UINT32)
         w.add(f"{a}.expert_used_count", cfg.n_expert_used, ValueType.UINT32)
     if vocab:

@@ -85,6 +85,12 @@ PRESETS: dict[str, ModelConfig] = {
     "tiny-qwen3": ModelConfig(name="tiny-qwen3", arch="qwen3", vocab_size=512, n_embd=256, n_layer=2, n_head=4, n_head_kv=2,
                               head_dim=128, n_ff=512, n_ctx_train=512, rope_theta=10000.0, rope_dim=128, rope_neox=True,
                               qk_norm=True),
+    "tiny-qwen3moe": ModelConfig(name="tiny-qwen3moe", arch="qwen3moe", vocab_size=512, n_embd=256, n_layer=2, n_head=4, n_head_kv=2,
+                                 head_dim=64, n_ff=256, n_ctx_train=512, rope_theta=10000.0, rope_dim=64, rope_neox=True, qk_norm=True,
+                                 n_expert=4, n_expert_used=2),
+    "qwen3-30b-a3b": ModelConfig(name="qwen3-30b-a3b", arch="qwen3moe", vocab_size=151936, n_embd=2048, n_layer=48, n_head=32, n_head_kv=4,
+                                 head_dim=128, n_ff=768, n_ctx_train=40960, rms_eps=1e-6, rope_theta=1000000.0, rope_dim=128,
+                                 rope_neox=True, qk_norm=True, n_expert=128, n_expert_used=8, bos_id=151643, eos_id=151645),
     "tiny-phi3": ModelConfig(name="tiny-phi3", arch="phi3", vocab_size=512, n_embd=256, n_layer=2, n_head=4, n_head_kv=4,
                              head_dim=64, n_ff=512, n_ctx_train=512, rope_theta=10000.0, rope_dim=64, rope_neox=True,
                              fused_qkv=True),
@@ -115,9 +121,10 @@ PRESETS: dict[str, ModelConfig] = {
 
 
 # GGUF `general.architecture` values this engine runs.  llama covers LLaMA 1-3, Mistral and Mixtral (MoE tensors present);
-# qwen2 adds Q/K/V biases, qwen3 per-head Q/K RMSNorm, phi3 fused QKV / gate-up tensors; the last three rotate half-split
+# qwen2 adds Q/K/V biases, qwen3 per-head Q/K RMSNorm (qwen3moe: the same attention with Mixtral-style routed experts of
+# `expert_feed_forward_length`), phi3 fused QKV / gate-up tensors; all but llama rotate half-split
 # ("neox") pairs (`llama.cpp/src/llama-model.cpp` llama_model_rope_type).
-SUPPORTED_ARCHS = {"llama", "qwen2", "qwen3", "phi3"}
+SUPPORTED_ARCHS = {"llama", "qwen2", "qwen3", "qwen3moe", "phi3"}
 
 
 def preset(name: str, **overrides) -> ModelConfig:
@@ -161,11 +168,12 @@ def config_from_gguf(meta: dict[str, Any], tensors: dict | None = None) -> Model
     return ModelConfig(
         name=str(meta.get("general.name", arch)), arch=arch, vocab_size=int(vocab), n_embd=n_embd,
         n_layer=int(g("block_count")), n_head=n_head, n_head_kv=n_head_kv, head_dim=head_dim,
-        n_ff=int(g("feed_forward_length")), n_ctx_train=int(g("context_length", 2048)),
+        n_ff=int(g("expert_feed_forward_length") or g("feed_forward_length")) if int(g("expert_count", 0) or 0) > 0 else int(g("feed_forward_length")),
+        n_ctx_train=int(g("context_length", 2048)),
         rms_eps=float(g("attention.layer_norm_rms_epsilon", 1e-5)), rope_theta=float(g("rope.freq_base", 10000.0)),
         rope_dim=int(g("rope.dimension_count", head_dim)), rope_neox=arch != "llama", rope_scale_linear=scale,
         qkv_bias=arch == "qwen2" or (tensors is not None and "blk.0.attn_q.bias" in tensors),
-        qk_norm=arch == "qwen3" or (tensors is not None and "blk.0.attn_q_norm.weight" in tensors),
+        qk_norm=arch in ("qwen3", "qwen3moe") or (tensors is not None and "blk.0.attn_q_norm.weight" in tensors),
         fused_qkv=arch == "phi3" or (tensors is not None and "blk.0.attn_qkv.weight" in tensors),
         n_expert=int(g("expert_count", 0) or 0), n_expert_used=int(g("expert_used_count", 0) or 0),
         bos_id=int(meta.get("tokenizer.ggml.bos_token_id", 1)), eos_id=int(meta.get("tokenizer.ggml.eos_token_id", 2)),
