@@ -36,10 +36,32 @@ def sse_event(msg_type: str, content: str) -> bytes:
 KEEPALIVE = b":\n\n"
 
 
+def _render_jinja(tmpl: str, messages: list[dict], meta: dict) -> str | None:
+    """Render the model's own Jinja chat template (what `common_chat_templates_apply` does through minja) in a sandbox; None when
+    jinja2 is missing or the template does not render (the marker-based fall-backs below take over)."""
+    try:
+        from jinja2.sandbox import ImmutableSandboxedEnvironment
+    except ImportError:
+        return None
+    try:
+        env = ImmutableSandboxedEnvironment(trim_blocks=True, lstrip_blocks=True)
+
+        def raise_exception(msg):
+            raise ValueError(msg)
+        env.globals["raise_exception"] = raise_exception
+        return env.from_string(tmpl).render(messages=messages, add_generation_prompt=True, bos_token=str(meta.get("bos_token", "")),
+                                            eos_token=str(meta.get("eos_token", "")))
+    except Exception:      # noqa: BLE001 - any template problem falls back to the built-in formats
+        return None
+
+
 def apply_chat_template(meta: dict, messages: list[dict]) -> str:
     """Minimal chat formatting: Llama-3 and ChatML families are recognised from the GGUF template string; models without a
     template (random-init checkpoints) get the plain concatenation.  (ref: built-in templates, `llama.cpp/src/llama-chat.cpp`)"""
     tmpl = str(meta.get("tokenizer.chat_template", ""))
+    rendered = _render_jinja(tmpl, messages, meta) if "{%" in tmpl or "{{" in tmpl else None
+    if rendered is not None:
+        return rendered
     if "<|start_header_id|>" in tmpl:
         out = "".join(f"<|start_header_id|>{m['role']}<|end_header_id|>\n\n{m['content']}<|eot_id|>" for m in messages)
         return out + "<|start_header_id|>assistant<|end_header_id|>\n\n"
@@ -652,7 +674,9 @@ def build_service(model: str, device: str = "cuda", n_ctx: int = 2048, n_slots: 
         f"kv cache: {eng.kv.n_pages} pages x {eng.page_size} tokens ({eng.kv.bytes() / 2**20:.1f} MiB), {n_slots} slots, n_ctx {n_ctx}\n",
     ]
     info = {"name": str(f.metadata.get("general.name", os.path.basename(model))), "n_params": cfg.n_params(), "n_ctx_train": cfg.n_ctx_train,
-            "metadata": {"tokenizer.chat_template": f.metadata.get("tokenizer.chat_template", "")}}
+            "metadata": {"tokenizer.chat_template": f.metadata.get("tokenizer.chat_template", ""),
+                         "bos_token": tok.tokens[tok.bos_id] if 0 <= tok.bos_id < tok.n_vocab else "",
+                         "eos_token": tok.tokens[tok.eos_id] if 0 <= tok.eos_id < tok.n_vocab else ""}}
     sched = Scheduler(eng, tok, n_batch=n_batch, n_slots=n_slots)
     return sched, info, logs
 

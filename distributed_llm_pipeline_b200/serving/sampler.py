@@ -3,7 +3,7 @@
 Parity: default chain order of the reference (`llama.cpp/common/common.h:201-210`, `common/sampling.cpp:179-311`):
 penalties -> top-k -> top-p -> min-p -> temperature -> dist.  Implemented samplers: repetition/frequency/presence
 penalties (`llama-sampling.cpp:2777`), top-k (`:1348`), top-p (`:1543`), min-p (`:1704`), typical (`:1814`),
-DRY (`:3216`), temperature (`:1918`), dynamic temperature (`temp_ext :2115`), XTC (`:2222`), mirostat v2 (`:2445`), top-n-sigma (`:2876`),
+DRY (`:3216`), temperature (`:1918`), dynamic temperature (`temp_ext :2115`), XTC (`:2222`), mirostat v1 / v2 (`:2341`, `:2445`), top-n-sigma (`:2876`),
 grammar (`:2625`, see grammar.py), greedy (`:1011`), seeded multinomial (`:1255`), logit bias (`:3455`).
 """
 from __future__ import annotations
@@ -31,7 +31,7 @@ class SamplingParams:
     dynatemp_exponent: float = 1.0
     xtc_probability: float = 0.0       # "exclude top choices": with this probability drop all but the least likely
     xtc_threshold: float = 0.1         # candidate whose probability is >= threshold
-    mirostat: int = 0                  # 2 = mirostat v2 (replaces top-k/top-p/min-p)
+    mirostat: int = 0                  # 1 = mirostat v1, 2 = mirostat v2 (both replace top-k/top-p/min-p)
     mirostat_tau: float = 5.0
     mirostat_eta: float = 0.1
     dry_multiplier: float = 0.0        # DRY ("don't repeat yourself"): penalty = multiplier * base^(match_len - allowed_length)
@@ -168,6 +168,24 @@ class Sampler:
             return int(row.argmax())
         if p.top_n_sigma > 0:
             row = row.masked_fill(row < row.max() - p.top_n_sigma * row.std(), float("-inf"))
+        if p.mirostat == 1:
+            # mirostat v1 (`llama-sampling.cpp:2341`): estimate the Zipf exponent s from the top candidates, derive the k that
+            # gives the target surprise, sample from the top-k, then move mu towards tau
+            vals, ids = torch.sort(row.float(), descending=True, stable=True)
+            probs = torch.softmax(vals / p.temperature, -1)
+            m = min(100, probs.numel() - 1)
+            i = torch.arange(m, dtype=torch.float32)
+            t = torch.log((i + 2) / (i + 1))
+            b = torch.log(probs[:m].clamp_min(1e-30) / probs[1:m + 1].clamp_min(1e-30))
+            s_hat = float((t * b).sum() / (t * t).sum().clamp_min(1e-30))
+            eps = s_hat - 1.0
+            n = float(probs.numel())
+            k = ((eps * (2.0 ** self.mu)) / (1.0 - n ** (-eps))) ** (1.0 / s_hat) if abs(eps) > 1e-6 else n
+            k = int(min(max(round(k), 1), probs.numel()))
+            pk = probs[:k] / probs[:k].sum()
+            j = int(torch.multinomial(pk, 1, generator=self.gen))
+            self.mu -= p.mirostat_eta * (float(-torch.log2(pk[j])) - p.mirostat_tau)
+            return int(ids[j])
         if p.mirostat == 2:
             probs = torch.softmax(row / p.temperature, -1)
             surprise = -torch.log2(probs.clamp_min(1e-30))

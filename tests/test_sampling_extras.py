@@ -143,3 +143,19 @@ def test_eval_callback_and_memory_breakdown(tmp_models):
     assert seen == [("l_out", 0, (3, 256)), ("l_out", 1, (3, 256)), ("l_out", 0, (1, 256)), ("l_out", 1, (1, 256))]
     mb = eng.memory_breakdown()
     assert mb["model"] > 0 and mb["kv_cache"] > 0 and mb["compute"] > 0
+
+
+def test_mirostat_v1_and_jinja_chat_template():
+    logits = torch.tensor([0.0, 0.1, 0.2, 3.0, 0.5, 2.0, 0.3, 5.0]) * 0.5
+    a = Sampler(SamplingParams(temperature=1.0, mirostat=1, mirostat_tau=2.0, seed=3))
+    b = Sampler(SamplingParams(temperature=1.0, mirostat=1, mirostat_tau=2.0, seed=3))
+    sa, sb = [a.sample(logits) for _ in range(40)], [b.sample(logits) for _ in range(40)]
+    assert sa == sb and len(set(sa)) > 1 and all(0 <= t < 8 for t in sa) and a.mu != 4.0
+    from distributed_llm_pipeline_b200.serving.orchestrator import apply_chat_template
+    tmpl = ("{{ bos_token }}{% for m in messages %}<|{{ m['role'] }}|>{{ m['content'] }}<|end|>{% endfor %}"
+            "{% if add_generation_prompt %}<|assistant|>{% endif %}")
+    msgs = [{"role": "system", "content": "S"}, {"role": "user", "content": "U"}]
+    assert apply_chat_template({"tokenizer.chat_template": tmpl, "bos_token": "<s>"}, msgs) == "<s><|system|>S<|end|><|user|>U<|end|><|assistant|>"
+    # a template that raises falls back to the marker-based formats
+    bad = "{% for m in messages %}{{ raise_exception('no') }}{% endfor %}<|im_start|>"
+    assert apply_chat_template({"tokenizer.chat_template": bad}, msgs).endswith("<|im_start|>assistant\n")

@@ -85,9 +85,13 @@ def main(argv=None):
         elif kind in ("log", "error"):
             log.info(content.rstrip("\n"))
 
+    history, last_prompt, last_reply = "", prompt, ""
     while True:
         req = sched.generate(prompt, n_predict=a.predict, sampling=sampling_from_args(a), ignore_eos=a.ignore_eos, on_event=on_event, n_keep=a.keep)
         sys.stdout.write("\n")
+        if not history:
+            history = prompt
+        last_reply = req.text + "\n"
         t = req.timings()
         log.info(f"prompt eval: {t['prompt_n']} tokens, {t['prompt_per_second']} tok/s | eval: {t['predicted_n']} tokens, {t['predicted_per_second']} tok/s")
         if a.single_turn or not sys.stdin.isatty():
@@ -96,8 +100,25 @@ def main(argv=None):
             prompt = input("> ")
         except EOFError:
             break
-        if prompt.strip() in ("/exit", "/quit"):
+        cmd = prompt.strip()
+        if cmd in ("/exit", "/quit"):
             break
+        if cmd == "/clear":                      # forget the conversation (and its cached prefix)
+            history = ""
+            sys.stderr.write("(conversation cleared)\n")
+            continue
+        if cmd == "/regen":                      # sample the last reply again
+            prompt = last_prompt
+        elif cmd.startswith("/read "):           # use a file's contents as the next message
+            try:
+                prompt = open(cmd[6:].strip()).read()
+            except OSError as e:
+                sys.stderr.write(f"cannot read file: {e}\n")
+                continue
+        if cmd != "/regen":
+            history = history + last_reply       # multi-turn: the reply becomes part of the next prompt (prefix stays cached)
+            prompt = history + prompt
+        last_prompt = prompt
     log.flush()
 
 
