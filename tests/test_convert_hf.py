@@ -1,0 +1,62 @@
+"""HF -> GGUF converter, cross-validated against an INDEPENDENT implementation: random-init Hugging Face models (transformers,
+CPU, fp32) are converted and the oracle / engine logits must match the HF forward pass - this pins the graph conventions
+(RoPE pair layout and the Q/K row permutation, bias, per-head Q/K norm, fused tensors, GQA) to the upstream definition."""
+import importlib
+import os
+import sys
+
+import pytest
+import torch
+
+REPO = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, os.path.join(REPO, "tools"))
+
+transformers = pytest.importorskip("transformers")
+pytest.importorskip("safetensors")
+
+COMMON = dict(vocab_size=512, hidden_size=256, intermediate_size=512, num_hidden_layers=2, num_attention_heads=4,
+              num_key_value_heads=2, max_position_embeddings=512, rms_norm_eps=1e-5, tie_word_embeddings=False,
+              bos_token_id=1, eos_token_id=2, pad_token_id=0)
+CASES = {
+    "llama": ("LlamaConfig", "LlamaForCausalLM", {}),
+    "mistral": ("MistralConfig", "MistralForCausalLM", {"sliding_window": None}),
+    "qwen2": ("Qwen2Config", "Qwen2ForCausalLM", {}),
+    "qwen3": ("Qwen3Config", "Qwen3ForCausalLM", {"head_dim": 128}),
+    "phi3": ("Phi3Config", "Phi3ForCausalLM", {"num_key_value_heads": 4}),
+    "mixtral": ("MixtralConfig", "MixtralForCausalLM", {"intermediate_size": 256, "num_local_experts": 4, "num_experts_per_tok": 2}),
+    "qwen3moe": ("Qwen3MoeConfig", "Qwen3MoeForCausalLM", {"head_dim": 64, "moe_intermediate_size": 128, "num_experts": 4,
+                                                             "num_experts_per_tok": 2, "norm_topk_prob": True}),
+}
+
+
+@pytest.mark.parametrize("family", list(CASES))
+def test_converted_model_matches_hf_forward(tmp_path, family):
+    cfg_cls, model_cls, extra = CASES[family]
+    if not hasattr(transformers, cfg_cls):
+        pytest.skip(f"transformers has no {cfg_cls}")
+    torch.manual_seed(0)
+    cfg = getattr(transformers, cfg_cls)(**{**COMMON, **extra})
+    model = getattr(transformers, model_cls)(cfg).eval().float()
+    with torch.no_grad():                      # make biases / norm weights non-trivial
+        for n, p in model.named_parameters():
+            if n.endswith("bias"):
+                p.normal_(0, 0.05)
+            elif "norm" in n:
+                p.copy_(1 + 0.1 * torch.randn_like(p))
+    d = tmp_path / family
+    model.save_pretrained(str(d), safe_serialization=True)
+    conv = importlib.import_module("convert_hf_to_gguf")
+    out = conv.convert(str(d), str(tmp_path / f"{family}.gguf"), "F32")
+    from distributed_llm_pipeline_b200.models.llama import LlamaEngine
+    from distributed_llm_pipeline_b200.models.reference import ReferenceModel, nmse
+    from distributed_llm_pipeline_b200.models.weights import load_weights
+    ids = [1, 5, 9, 200, 33, 7, 8, 100, 42, 17, 3, 250]
+    with torch.no_grad():
+        want = model(torch.tensor([ids])).logits[0]
+    ref = ReferenceModel.from_gguf(out)
+    assert ref.cfg.arch == ("llama" if family in ("llama", "mistral", "mixtral") else family)
+    got = ref.forward(ids, ref.new_cache(32))
+    assert nmse(want, got) < 1e-9, family
+    eng = LlamaEngine(load_weights(out, "cpu"), n_ctx=64, max_seqs=1, page_size=16, max_batch_tokens=32)
+    lg = eng.prefill(eng.alloc_seq(), ids)
+    assert nmse(want[-1], lg.float().flatten()) < 1e-5

@@ -1,0 +1,226 @@
+#!/usr/bin/env python
+"""convert-hf-to-gguf: Hugging Face checkpoint directory (config.json + *.safetensors) -> GGUF.
+
+Parity: `llama.cpp/convert_hf_to_gguf.py` for the architecture families this engine runs: LlamaForCausalLM / MistralForCausalLM
+/ MixtralForCausalLM (arch `llama`, Q/K rows permuted from the HF half-split layout to ggml's adjacent-pair rotation; experts
+stacked into `ffn_*_exps`), Qwen2ForCausalLM (`qwen2`, biases), Qwen3ForCausalLM / Qwen3MoeForCausalLM (`qwen3`, `qwen3moe`,
+per-head Q/K norms), Phi3ForCausalLM (`phi3`, fused qkv / gate_up kept fused).
+Tokenizer: `tokenizer.json` (byte-level BPE -> `gpt2` model with merges) or `tokenizer.model` (SentencePiece -> `llama` model)
+when present, else a synthetic vocabulary (random-init test checkpoints).  Output types: F32 / F16 / BF16 / Q8_0.
+"""
+import argparse
+import json
+import os
+import re
+import sys
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import numpy as np  # noqa: E402
+
+from distributed_llm_pipeline_b200.gguf import GGMLType, GGUFWriter, quantize  # noqa: E402
+from distributed_llm_pipeline_b200.gguf.constants import FTYPE, TokenType, ValueType  # noqa: E402
+from distributed_llm_pipeline_b200.gguf.synth import synthetic_vocab  # noqa: E402
+
+ARCHS = {"LlamaForCausalLM": "llama", "MistralForCausalLM": "llama", "MixtralForCausalLM": "llama", "Qwen2ForCausalLM": "qwen2",
+         "Qwen3ForCausalLM": "qwen3", "Qwen3MoeForCausalLM": "qwen3moe", "Phi3ForCausalLM": "phi3"}
+LAYER_MAP = {
+    "input_layernorm.weight": "attn_norm.weight", "post_attention_layernorm.weight": "ffn_norm.weight",
+    "self_attn.q_proj.weight": "attn_q.weight", "self_attn.k_proj.weight": "attn_k.weight", "self_attn.v_proj.weight": "attn_v.weight",
+    "self_attn.q_proj.bias": "attn_q.bias", "self_attn.k_proj.bias": "attn_k.bias", "self_attn.v_proj.bias": "attn_v.bias",
+    "self_attn.o_proj.weight": "attn_output.weight", "self_attn.q_norm.weight": "attn_q_norm.weight",
+    "self_attn.k_norm.weight": "attn_k_norm.weight", "self_attn.qkv_proj.weight": "attn_qkv.weight",
+    "mlp.gate_proj.weight": "ffn_gate.weight", "mlp.up_proj.weight": "ffn_up.weight", "mlp.down_proj.weight": "ffn_down.weight",
+    "mlp.gate_up_proj.weight": "ffn_up.weight",
+}
+TOP_MAP = {"model.embed_tokens.weight": "token_embd.weight", "model.norm.weight": "output_norm.weight", "lm_head.weight": "output.weight"}
+
+
+def permute_qk(w: np.ndarray, n_head: int) -> np.ndarray:
+    """HF stores Q/K rows for rotate_half (first half | second half of every head); ggml's llama graph rotates adjacent pairs."""
+    return w.reshape(n_head, 2, w.shape[0] // n_head // 2, *w.shape[1:]).swapaxes(1, 2).reshape(w.shape)
+
+
+def load_safetensors(d: str) -> dict:
+    from safetensors import safe_open
+    out = {}
+    for fn in sorted(os.listdir(d)):
+        if fn.endswith(".safetensors"):
+            with safe_open(os.path.join(d, fn), framework="pt") as f:
+                for k in f.keys():
+                    out[k] = f.get_tensor(k)
+    return out
+
+
+def add_tokenizer(w: GGUFWriter, d: str, n_vocab: int, cfg: dict):
+    tj, tm = os.path.join(d, "tokenizer.json"), os.path.join(d, "tokenizer.model")
+    bos, eos = cfg.get("bos_token_id"), cfg.get("eos_token_id")
+    eos = eos[0] if isinstance(eos, list) else eos
+    if os.path.exists(tj):
+        t = json.load(open(tj))
+        model = t.get("model", {})
+        if model.get("type") == "BPE":
+            vocab = model["vocab"]
+            toks = [f"[PAD{i}]" for i in range(n_vocab)]
+            types = [int(TokenType.UNUSED)] * n_vocab
+            for s, i in vocab.items():
+                if i < n_vocab:
+                    toks[i], types[i] = s, int(TokenType.NORMAL)
+            for a in t.get("added_tokens", []):
+                if a["id"] < n_vocab:
+                    toks[a["id"]], types[a["id"]] = a["content"], int(TokenType.CONTROL if a.get("special") else TokenType.USER_DEFINED)
+            merges = [m if isinstance(m, str) else " ".join(m) for m in model.get("merges", [])]
+            w.add("tokenizer.ggml.model", "gpt2")
+            w.add("tokenizer.ggml.pre", "llama-bpe" if "llama" in str(cfg.get("model_type", "")) else "default")
+            w.add("tokenizer.ggml.tokens", toks, etype=ValueType.STRING)
+            w.add("tokenizer.ggml.token_type", np.asarray(types, np.int32), etype=ValueType.INT32)
+            w.add("tokenizer.ggml.merges", merges, etype=ValueType.STRING)
+            _ids(w, bos, eos)
+            return "bpe"
+    if os.path.exists(tm):
+        import sentencepiece as spm
+        sp = spm.SentencePieceProcessor(model_file=tm)
+        toks, scores, types = [], [], []
+        for i in range(n_vocab):
+            if i < sp.get_piece_size():
+                toks.append(sp.id_to_piece(i))
+                scores.append(sp.get_score(i))
+                types.append(int(TokenType.CONTROL if sp.is_control(i) else TokenType.UNKNOWN if sp.is_unknown(i)
+                                 else TokenType.BYTE if sp.is_byte(i) else TokenType.NORMAL))
+            else:
+                toks.append(f"[PAD{i}]"); scores.append(-1000.0); types.append(int(TokenType.UNUSED))
+        w.add("tokenizer.ggml.model", "llama")
+        w.add("tokenizer.ggml.tokens", toks, etype=ValueType.STRING)
+        w.add("tokenizer.ggml.scores", np.asarray(scores, np.float32), etype=ValueType.FLOAT32)
+        w.add("tokenizer.ggml.token_type", np.asarray(types, np.int32), etype=ValueType.INT32)
+        _ids(w, bos, eos)
+        return "spm"
+    toks, scores, types = synthetic_vocab(n_vocab)
+    w.add("tokenizer.ggml.model", "llama")
+    w.add("tokenizer.ggml.tokens", toks, etype=ValueType.STRING)
+    w.add("tokenizer.ggml.scores", scores, etype=ValueType.FLOAT32)
+    w.add("tokenizer.ggml.token_type", types, etype=ValueType.INT32)
+    _ids(w, 1, 2)
+    return "synthetic"
+
+
+def _ids(w, bos, eos):
+    if bos is not None:
+        w.add("tokenizer.ggml.bos_token_id", int(bos), ValueType.UINT32)
+    if eos is not None:
+        w.add("tokenizer.ggml.eos_token_id", int(eos), ValueType.UINT32)
+
+
+def convert(src: str, dst: str, outtype: str = "F16") -> str:
+    cfg = json.load(open(os.path.join(src, "config.json")))
+    hf_arch = (cfg.get("architectures") or ["?"])[0]
+    if hf_arch not in ARCHS:
+        raise SystemExit(f"unsupported architecture {hf_arch}; supported: {sorted(ARCHS)}")
+    a = ARCHS[hf_arch]
+    E, L = cfg["hidden_size"], cfg["num_hidden_layers"]
+    H = cfg["num_attention_heads"]
+    Hkv = cfg.get("num_key_value_heads") or H
+    D = cfg.get("head_dim") or E // H
+    rope = cfg.get("rope_parameters") or {}
+    theta = float(cfg.get("rope_theta") or rope.get("rope_theta") or 10000.0)
+    w = GGUFWriter(dst)
+    w.add("general.architecture", a)
+    w.add("general.name", os.path.basename(os.path.normpath(src)))
+    w.add("general.file_type", FTYPE[outtype], ValueType.UINT32)
+    w.add(f"{a}.vocab_size", cfg["vocab_size"], ValueType.UINT32)
+    w.add(f"{a}.context_length", cfg.get("max_position_embeddings", 2048), ValueType.UINT32)
+    w.add(f"{a}.embedding_length", E, ValueType.UINT32)
+    w.add(f"{a}.block_count", L, ValueType.UINT32)
+    w.add(f"{a}.feed_forward_length", cfg["intermediate_size"], ValueType.UINT32)
+    n_exp = int(cfg.get("num_local_experts") or cfg.get("num_experts") or 0)
+    if n_exp:
+        w.add(f"{a}.expert_count", n_exp, ValueType.UINT32)
+        w.add(f"{a}.expert_used_count", int(cfg.get("num_experts_per_tok", 2)), ValueType.UINT32)
+        if cfg.get("moe_intermediate_size"):
+            w.add(f"{a}.expert_feed_forward_length", int(cfg["moe_intermediate_size"]), ValueType.UINT32)
+    w.add(f"{a}.attention.head_count", H, ValueType.UINT32)
+    w.add(f"{a}.attention.head_count_kv", Hkv, ValueType.UINT32)
+    w.add(f"{a}.attention.layer_norm_rms_epsilon", float(cfg.get("rms_norm_eps", 1e-5)), ValueType.FLOAT32)
+    w.add(f"{a}.rope.freq_base", theta, ValueType.FLOAT32)
+    w.add(f"{a}.rope.dimension_count", D, ValueType.UINT32)
+    if D * H != E:
+        w.add(f"{a}.attention.key_length", D, ValueType.UINT32)
+        w.add(f"{a}.attention.value_length", D, ValueType.UINT32)
+    sc = cfg.get("rope_scaling") or (rope if rope.get("rope_type") not in (None, "default") else None)
+    if sc:
+        kind = sc.get("rope_type") or sc.get("type")
+        if kind in ("linear", "yarn"):
+            w.add(f"{a}.rope.scaling.type", kind)
+            w.add(f"{a}.rope.scaling.factor", float(sc.get("factor", 1.0)), ValueType.FLOAT32)
+            if kind == "yarn" and sc.get("original_max_position_embeddings"):
+                w.add(f"{a}.rope.scaling.original_context_length", int(sc["original_max_position_embeddings"]), ValueType.UINT32)
+    tok_kind = add_tokenizer(w, src, cfg["vocab_size"], cfg)
+    tensors = load_safetensors(src)
+    qtype = {"F32": GGMLType.F32, "F16": GGMLType.F16, "BF16": GGMLType.BF16, "Q8_0": GGMLType.Q8_0}[outtype]
+    n = 0
+    # routed experts: either fused 3-D tensors (transformers >= 5: experts.gate_up_proj [n, 2F, E], experts.down_proj [n, E, F]) or
+    # one matrix per expert (experts.<e>.w1/w3/w2 or .gate_proj/.up_proj/.down_proj) -> stacked ffn_{gate,up,down}_exps
+    moe: dict[str, dict[str, dict[int, np.ndarray]]] = {}
+    for name in list(tensors):
+        m = re.match(r"model\.layers\.(\d+)\.(?:mlp|block_sparse_moe)\.(.+)", name)
+        if not m or not n_exp:
+            continue
+        il, rest = m.group(1), m.group(2)
+        t = tensors[name]
+        if rest == "gate.weight":
+            tensors[f"__moe__.blk.{il}.ffn_gate_inp.weight"] = tensors.pop(name)
+        elif rest == "experts.gate_up_proj":
+            g, u = t.float().chunk(2, dim=1)
+            tensors[f"__moe__.blk.{il}.ffn_gate_exps.weight"], tensors[f"__moe__.blk.{il}.ffn_up_exps.weight"] = g.contiguous(), u.contiguous()
+            tensors.pop(name)
+        elif rest == "experts.down_proj":
+            tensors[f"__moe__.blk.{il}.ffn_down_exps.weight"] = tensors.pop(name)
+        else:
+            me = re.match(r"experts\.(\d+)\.(w1|w2|w3|gate_proj|up_proj|down_proj)\.weight", rest)
+            if me:
+                kind = {"w1": "gate", "gate_proj": "gate", "w3": "up", "up_proj": "up", "w2": "down", "down_proj": "down"}[me.group(2)]
+                moe.setdefault(il, {}).setdefault(kind, {})[int(me.group(1))] = tensors.pop(name).float().numpy()
+    for il, kinds in moe.items():
+        for kind, per in kinds.items():
+            import torch
+            tensors[f"__moe__.blk.{il}.ffn_{kind}_exps.weight"] = torch.from_numpy(np.stack([per[e] for e in range(n_exp)]))
+    for name in sorted(tensors, key=lambda k: (0 if k.startswith("model.embed") else 1, [int(x) if x.isdigit() else x for x in re.split(r"(\d+)", k)])):
+        if name.endswith("rotary_emb.inv_freq"):
+            continue
+        if name.startswith("__moe__."):
+            out = name[len("__moe__."):]
+        elif name in TOP_MAP:
+            out = TOP_MAP[name]
+        else:
+            m = re.match(r"model\.layers\.(\d+)\.(.+)", name)
+            if not m or m.group(2) not in LAYER_MAP:
+                raise SystemExit(f"unmapped tensor {name}")
+            out = f"blk.{m.group(1)}.{LAYER_MAP[m.group(2)]}"
+        if name == "lm_head.weight" and cfg.get("tie_word_embeddings"):
+            continue
+        t = tensors[name].float().numpy()
+        if a == "llama" and out.endswith("attn_q.weight"):
+            t = permute_qk(t, H)
+        if a == "llama" and out.endswith("attn_k.weight"):
+            t = permute_qk(t, Hkv)
+        ttype = qtype if t.ndim >= 2 and not out.endswith("_norm.weight") and not out.endswith("ffn_gate_inp.weight") else GGMLType.F32
+        if ttype == GGMLType.Q8_0 and t.shape[-1] % 32:
+            ttype = GGMLType.F16
+        arr = np.ascontiguousarray(t)
+        w.add_tensor(out, arr.shape, ttype, lambda arr=arr, ttype=ttype: quantize(arr.reshape(-1, arr.shape[-1]) if arr.ndim > 1 else arr, ttype))
+        n += 1
+    w.write()
+    print(f"{src} ({hf_arch}) -> {dst}: arch {a}, {n} tensors, {outtype}, tokenizer {tok_kind}")
+    return dst
+
+
+def main(argv=None):
+    ap = argparse.ArgumentParser(description=__doc__.splitlines()[0])
+    ap.add_argument("model_dir")
+    ap.add_argument("--outfile", required=True)
+    ap.add_argument("--outtype", default="F16", choices=["F32", "F16", "BF16", "Q8_0"])
+    a = ap.parse_args(argv)
+    convert(a.model_dir, a.outfile, a.outtype)
+
+
+if __name__ == "__main__":
+    main()
