@@ -19,8 +19,13 @@ COMMON = dict(vocab_size=512, hidden_size=256, intermediate_size=512, num_hidden
               bos_token_id=1, eos_token_id=2, pad_token_id=0)
 CASES = {
     "llama": ("LlamaConfig", "LlamaForCausalLM", {}),
+    "llama31": ("LlamaConfig", "LlamaForCausalLM", {"rope_parameters": {"rope_type": "llama3", "rope_theta": 10000.0, "factor": 8.0,
+                                                                          "low_freq_factor": 1.0, "high_freq_factor": 4.0,
+                                                                          "original_max_position_embeddings": 64}}),
     "mistral": ("MistralConfig", "MistralForCausalLM", {"sliding_window": None}),
     "qwen2": ("Qwen2Config", "Qwen2ForCausalLM", {}),
+    "qwen2-yarn": ("Qwen2Config", "Qwen2ForCausalLM", {"rope_parameters": {"rope_type": "yarn", "rope_theta": 10000.0, "factor": 4.0,
+                                                                             "original_max_position_embeddings": 128}}),
     "qwen3": ("Qwen3Config", "Qwen3ForCausalLM", {"head_dim": 128}),
     "phi3": ("Phi3Config", "Phi3ForCausalLM", {"num_key_value_heads": 4}),
     "mixtral": ("MixtralConfig", "MixtralForCausalLM", {"intermediate_size": 256, "num_local_experts": 4, "num_experts_per_tok": 2}),
@@ -50,12 +55,16 @@ def test_converted_model_matches_hf_forward(tmp_path, family):
     from distributed_llm_pipeline_b200.models.llama import LlamaEngine
     from distributed_llm_pipeline_b200.models.reference import ReferenceModel, nmse
     from distributed_llm_pipeline_b200.models.weights import load_weights
-    ids = [1, 5, 9, 200, 33, 7, 8, 100, 42, 17, 3, 250]
+    ids = [1, 5, 9, 200, 33, 7, 8, 100, 42, 17, 3, 250] * (4 if "yarn" in family else 1)
     with torch.no_grad():
         want = model(torch.tensor([ids])).logits[0]
     ref = ReferenceModel.from_gguf(out)
-    assert ref.cfg.arch == ("llama" if family in ("llama", "mistral", "mixtral") else family)
-    got = ref.forward(ids, ref.new_cache(32))
+    assert ref.cfg.arch == ("llama" if family in ("llama", "llama31", "mistral", "mixtral") else family.split("-")[0])
+    if family == "qwen2-yarn":
+        assert ref.cfg.yarn_factor == 4.0 and ref.cfg.yarn_orig_ctx == 128
+    if family == "llama31":
+        assert "rope_freqs.weight" in ref.w and float(ref.w["rope_freqs.weight"].max()) == 8.0
+    got = ref.forward(ids, ref.new_cache(64))
     assert nmse(want, got) < 1e-9, family
     eng = LlamaEngine(load_weights(out, "cpu"), n_ctx=64, max_seqs=1, page_size=16, max_batch_tokens=32)
     lg = eng.prefill(eng.alloc_seq(), ids)

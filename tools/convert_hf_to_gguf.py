@@ -153,6 +153,25 @@ def convert(src: str, dst: str, outtype: str = "F16") -> str:
             w.add(f"{a}.rope.scaling.factor", float(sc.get("factor", 1.0)), ValueType.FLOAT32)
             if kind == "yarn" and sc.get("original_max_position_embeddings"):
                 w.add(f"{a}.rope.scaling.original_context_length", int(sc["original_max_position_embeddings"]), ValueType.UINT32)
+    rope_factors = None
+    if sc and (sc.get("rope_type") or sc.get("type")) == "llama3":
+        # Llama-3.1 / 3.2 frequency-dependent scaling becomes a per-frequency divisor tensor (`rope_freqs.weight`), exactly as
+        # the reference converter does: long wavelengths are divided by `factor`, short ones kept, a smooth ramp in between
+        import math
+        factor, lo, hi = float(sc.get("factor", 8.0)), float(sc.get("low_freq_factor", 1.0)), float(sc.get("high_freq_factor", 4.0))
+        old_ctx = float(sc.get("original_max_position_embeddings", 8192))
+        freqs = theta ** (-np.arange(0, D, 2, dtype=np.float64) / D)
+        out = []
+        for f in freqs:
+            wavelen = 2 * math.pi / f
+            if wavelen < old_ctx / hi:
+                out.append(1.0)
+            elif wavelen > old_ctx / lo:
+                out.append(factor)
+            else:
+                smooth = (old_ctx / wavelen - lo) / (hi - lo)
+                out.append(1.0 / ((1.0 - smooth) / factor + smooth))
+        rope_factors = np.asarray(out, dtype="<f4")
     tok_kind = add_tokenizer(w, src, cfg["vocab_size"], cfg)
     tensors = load_safetensors(src)
     qtype = {"F32": GGMLType.F32, "F16": GGMLType.F16, "BF16": GGMLType.BF16, "Q8_0": GGMLType.Q8_0}[outtype]
@@ -208,6 +227,8 @@ def convert(src: str, dst: str, outtype: str = "F16") -> str:
         arr = np.ascontiguousarray(t)
         w.add_tensor(out, arr.shape, ttype, lambda arr=arr, ttype=ttype: quantize(arr.reshape(-1, arr.shape[-1]) if arr.ndim > 1 else arr, ttype))
         n += 1
+    if rope_factors is not None:
+        w.add_tensor("rope_freqs.weight", rope_factors.shape, GGMLType.F32, lambda: rope_factors.view(np.uint8).reshape(-1))
     w.write()
     print(f"{src} ({hf_arch}) -> {dst}: arch {a}, {n} tensors, {outtype}, tokenizer {tok_kind}")
     return dst
