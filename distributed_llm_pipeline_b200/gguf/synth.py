@@ -173,6 +173,14 @@ def write_synthetic_gguf(path: str, cfg: ModelConfig, ftype: str = "F16", seed: 
     if cfg.head_dim * cfg.n_head != cfg.n_embd:
         w.add(f"{a}.attention.key_length", cfg.head_dim, ValueType.UINT32)
         w.add(f"{a}.attention.value_length", cfg.head_dim, ValueType.UINT32)
+    if cfg.embedding_scale != 1.0:
+        w.add(f"{a}.embedding_scale", float(cfg.embedding_scale), ValueType.FLOAT32)
+    if cfg.residual_scale != 1.0:
+        w.add(f"{a}.residual_scale", float(cfg.residual_scale), ValueType.FLOAT32)
+    if cfg.logit_scale != 1.0:
+        w.add(f"{a}.logit_scale", float(cfg.logit_scale), ValueType.FLOAT32)
+    if cfg.attention_scale > 0.0:
+        w.add(f"{a}.attention.scale", float(cfg.attention_scale), ValueType.FLOAT32)
     if cfg.yarn_factor > 1.0:
         w.add(f"{a}.rope.scaling.type", "yarn")
         w.add(f"{a}.rope.scaling.factor", float(cfg.yarn_factor), ValueType.FLOAT32)

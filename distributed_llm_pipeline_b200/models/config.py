@@ -42,6 +42,11 @@ class ModelConfig:
     qkv_bias: bool = False     # qwen2: bias on Wq/Wk/Wv
     qk_norm: bool = False      # qwen3: per-head RMSNorm on Q and K before RoPE
     fused_qkv: bool = False    # phi3: one attn_qkv tensor and one [2*n_ff] ffn_up (gate | up) tensor in the file
+    # granite: four scalar multipliers on top of the llama graph (`llama.cpp/src/models/granite.cpp`, keys `llama-arch.cpp`)
+    embedding_scale: float = 1.0   # h = embed(tok) * embedding_scale
+    residual_scale: float = 1.0    # h += residual_scale * block(h)
+    logit_scale: float = 1.0       # logits /= logit_scale
+    attention_scale: float = 0.0   # replaces 1/sqrt(head_dim) when > 0
 
     @property
     def n_gqa(self) -> int:
@@ -91,6 +96,12 @@ PRESETS: dict[str, ModelConfig] = {
     "qwen3-30b-a3b": ModelConfig(name="qwen3-30b-a3b", arch="qwen3moe", vocab_size=151936, n_embd=2048, n_layer=48, n_head=32, n_head_kv=4,
                                  head_dim=128, n_ff=768, n_ctx_train=40960, rms_eps=1e-6, rope_theta=1000000.0, rope_dim=128,
                                  rope_neox=True, qk_norm=True, n_expert=128, n_expert_used=8, bos_id=151643, eos_id=151645),
+    "tiny-granite": ModelConfig(name="tiny-granite", arch="granite", vocab_size=512, n_embd=256, n_layer=2, n_head=4, n_head_kv=2,
+                                head_dim=64, n_ff=512, n_ctx_train=512, rope_theta=10000.0, rope_dim=64, embedding_scale=12.0,
+                                residual_scale=0.22, logit_scale=8.0, attention_scale=0.015625),
+    "granite-3-8b": ModelConfig(name="granite-3-8b", arch="granite", vocab_size=49155, n_embd=4096, n_layer=40, n_head=32, n_head_kv=8,
+                                head_dim=128, n_ff=12800, n_ctx_train=4096, rope_theta=10000.0, rope_dim=128, embedding_scale=12.0,
+                                residual_scale=0.22, logit_scale=16.0, attention_scale=0.0078125),
     "tiny-phi3": ModelConfig(name="tiny-phi3", arch="phi3", vocab_size=512, n_embd=256, n_layer=2, n_head=4, n_head_kv=4,
                              head_dim=64, n_ff=512, n_ctx_train=512, rope_theta=10000.0, rope_dim=64, rope_neox=True,
                              fused_qkv=True),
@@ -124,7 +135,7 @@ PRESETS: dict[str, ModelConfig] = {
 # qwen2 adds Q/K/V biases, qwen3 per-head Q/K RMSNorm (qwen3moe: the same attention with Mixtral-style routed experts of
 # `expert_feed_forward_length`), phi3 fused QKV / gate-up tensors; all but llama rotate half-split
 # ("neox") pairs (`llama.cpp/src/llama-model.cpp` llama_model_rope_type).
-SUPPORTED_ARCHS = {"llama", "qwen2", "qwen3", "qwen3moe", "phi3"}
+SUPPORTED_ARCHS = {"llama", "qwen2", "qwen3", "qwen3moe", "phi3", "granite"}
 
 
 def preset(name: str, **overrides) -> ModelConfig:
@@ -171,7 +182,9 @@ def config_from_gguf(meta: dict[str, Any], tensors: dict | None = None) -> Model
         n_ff=int(g("expert_feed_forward_length") or g("feed_forward_length")) if int(g("expert_count", 0) or 0) > 0 else int(g("feed_forward_length")),
         n_ctx_train=int(g("context_length", 2048)),
         rms_eps=float(g("attention.layer_norm_rms_epsilon", 1e-5)), rope_theta=float(g("rope.freq_base", 10000.0)),
-        rope_dim=int(g("rope.dimension_count", head_dim)), rope_neox=arch != "llama", rope_scale_linear=scale,
+        rope_dim=int(g("rope.dimension_count", head_dim)), rope_neox=arch not in ("llama", "granite"), rope_scale_linear=scale,
+        embedding_scale=float(g("embedding_scale", 1.0) or 1.0), residual_scale=float(g("residual_scale", 1.0) or 1.0),
+        logit_scale=float(g("logit_scale", 1.0) or 1.0), attention_scale=float(g("attention.scale", 0.0) or 0.0),
         qkv_bias=arch == "qwen2" or (tensors is not None and "blk.0.attn_q.bias" in tensors),
         qk_norm=arch in ("qwen3", "qwen3moe") or (tensors is not None and "blk.0.attn_q_norm.weight" in tensors),
         fused_qkv=arch == "phi3" or (tensors is not None and "blk.0.attn_qkv.weight" in tensors),

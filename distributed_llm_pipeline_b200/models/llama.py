@@ -406,6 +406,8 @@ class LlamaEngine:
     # ---- stage-level forward ------------------------------------------------------------------
     def _embed(self, T: int, ids: torch.Tensor | None = None):
         ops.dequant_rows(self.w.tok_embd, self.tokens[:T] if ids is None else ids, out=self.h[:T])
+        if self.cfg.embedding_scale != 1.0:
+            self.h[:T].mul_(self.cfg.embedding_scale)
 
     def _run_layers(self, T: int, attn_fn, fused: bool = False):
         if fused:
@@ -469,6 +471,8 @@ class LlamaEngine:
         if nv > 0:
             if self.first_stage:
                 ops.dequant_rows(w.tok_embd, self.tokens[r0:r0 + nv], out=hs[:nv])
+                if cfg.embedding_scale != 1.0:
+                    hs[:nv].mul_(cfg.embedding_scale)
             else:
                 hs[:nv].copy_(self.h[r0:r0 + nv])
         if Tp > T:

@@ -49,9 +49,10 @@ def rope_inv_freq(cfg: ModelConfig, freq_factors: torch.Tensor | None = None) ->
 def rope_attn_scale(cfg: ModelConfig) -> float:
     """Multiplier on the attention logits from YaRN's magnitude correction (cos/sin are scaled by
     mscale = attn_factor * (1 + 0.1 ln(factor)) on both Q and K, i.e. the scores by mscale^2)."""
+    base = cfg.attention_scale * math.sqrt(cfg.head_dim) if cfg.attention_scale > 0.0 else 1.0   # granite: explicit score scale
     if cfg.yarn_factor <= 1.0 or cfg.yarn_ext_factor == 0.0:
-        return 1.0
-    return (cfg.yarn_attn_factor * (1.0 + 0.1 * math.log(cfg.yarn_factor))) ** 2
+        return base
+    return base * (cfg.yarn_attn_factor * (1.0 + 0.1 * math.log(cfg.yarn_factor))) ** 2
 
 
 def apply_rope(x: torch.Tensor, pos: torch.Tensor, inv_freq: torch.Tensor, neox: bool) -> torch.Tensor:
@@ -167,17 +168,17 @@ class ReferenceModel:
     def layer(self, il: int, h: torch.Tensor, pos: torch.Tensor, cache: RefKVCache) -> torch.Tensor:
         c, w = self.cfg, self.w
         p = f"blk.{il}."
-        h = h + self.attention(il, rms_norm(h, w[p + "attn_norm.weight"], c.rms_eps), pos, cache)
-        h = h + self.ffn(il, rms_norm(h, w[p + "ffn_norm.weight"], c.rms_eps))
+        h = h + c.residual_scale * self.attention(il, rms_norm(h, w[p + "attn_norm.weight"], c.rms_eps), pos, cache)
+        h = h + c.residual_scale * self.ffn(il, rms_norm(h, w[p + "ffn_norm.weight"], c.rms_eps))
         return h
 
     def embed(self, tokens: torch.Tensor) -> torch.Tensor:
-        return self.w["token_embd.weight"][tokens]
+        return self.w["token_embd.weight"][tokens] * self.cfg.embedding_scale
 
     def head(self, h: torch.Tensor) -> torch.Tensor:
         c, w = self.cfg, self.w
         out_w = w.get("output.weight", w["token_embd.weight"])
-        return rms_norm(h, w["output_norm.weight"], c.rms_eps) @ out_w.T
+        return rms_norm(h, w["output_norm.weight"], c.rms_eps) @ out_w.T / c.logit_scale
 
     # ---- full forward ---------------------------------------------------------------------
     @torch.no_grad()

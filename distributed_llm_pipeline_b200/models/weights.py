@@ -16,7 +16,7 @@ import numpy as np
 import torch
 
 from ..gguf import GGMLType, GGUFModelFiles, open_gguf
-from ..ops.weights import DeviceWeight, slice_raw, stack_rows
+from ..ops.weights import DeviceWeight, scale_raw, slice_raw, stack_rows
 from .config import ModelConfig, config_from_gguf
 
 
@@ -144,31 +144,37 @@ def load_weights(src: str | GGUFModelFiles, device, layer_range: range | None = 
     def f32(name):
         return torch.from_numpy(np.array(f.array(name), dtype=np.float32, copy=True)).to(dev)
 
-    def mat(name, rows=None, cols=None, sub=None) -> DeviceWeight:
+    def mat(name, rows=None, cols=None, sub=None, scale: float = 1.0) -> DeviceWeight:
         t = f.tensors[name]
         raw = f.raw(name)
         shape = t.shape
+        ttype = t.ggml_type
         if sub is not None:  # one expert of a stacked [n_expert, N, K] tensor
             raw = raw[sub]
             shape = shape[1:]
         deltas = [d for d in (ad.delta(name) for ad in lora) if d is not None] if sub is None else []
+        if scale != 1.0 and not deltas:       # scalar folded into the matrix (granite residual multiplier): block scales only
+            raw, ttype = scale_raw(raw, ttype, shape, scale)
+            scale = 1.0
         try:
             if deltas:
                 raise ValueError("LoRA target: merge densely")
-            raw2, shp = slice_raw(raw, t.ggml_type, shape, rows, cols)
+            raw2, shp = slice_raw(raw, ttype, shape, rows, cols)
         except ValueError:
             # K range not aligned to the quant block (tiny models / odd TP sizes): decode once, slice densely, keep fp16
             from ..gguf.quants import dequantize, quantize
-            dense = dequantize(raw, t.ggml_type, shape)
+            dense = dequantize(raw, ttype, shape)
             for d in deltas:
                 dense = dense + d.reshape(dense.shape)
+            if scale != 1.0:
+                dense = dense * np.float32(scale)
             if rows is not None:
                 dense = dense[rows[0]:rows[1]]
             if cols is not None:
                 dense = dense[:, cols[0]:cols[1]]
             dense = np.ascontiguousarray(dense)
             return DeviceWeight.from_raw(quantize(dense, GGMLType.F16), GGMLType.F16, dense.shape, dev)
-        return DeviceWeight.from_raw(raw2, t.ggml_type, shp, dev)
+        return DeviceWeight.from_raw(raw2, ttype, shp, dev)
 
     layers: dict[int, LayerWeights] = {}
     for il in layer_range:
@@ -199,7 +205,7 @@ def load_weights(src: str | GGUFModelFiles, device, layer_range: range | None = 
             wqkv = (DeviceWeight(GGMLType.F16, dense.shape[0], dense.shape[1], [], dense) if dev.type == "cpu"
                     else DeviceWeight(GGMLType.F16, dense.shape[0], dense.shape[1], [dense.to(torch.float16).contiguous()]))
         lw = LayerWeights(attn_norm=f32(p + "attn_norm.weight"), wqkv=wqkv, wv=wv_sep,
-                          wo=mat(p + "attn_output.weight", cols=(hq0 * D, hq1 * D)), ffn_norm=f32(p + "ffn_norm.weight"))
+                          wo=mat(p + "attn_output.weight", cols=(hq0 * D, hq1 * D), scale=cfg.residual_scale), ffn_norm=f32(p + "ffn_norm.weight"))
         if cfg.qkv_bias:
             lw.qkv_bias = torch.cat([f32(p + "attn_q.bias")[qr[0]:qr[1]], f32(p + "attn_k.bias")[kr[0]:kr[1]],
                                      f32(p + "attn_v.bias")[kr[0]:kr[1]]]).contiguous()
@@ -209,7 +215,7 @@ def load_weights(src: str | GGUFModelFiles, device, layer_range: range | None = 
         if cfg.fused_qkv:   # phi3: ffn_up rows [gate | up]
             lw.w_gate = mat(p + "ffn_up.weight", rows=(f0, f1))
             lw.w_up = mat(p + "ffn_up.weight", rows=(cfg.n_ff + f0, cfg.n_ff + f1))
-            lw.w_down = mat(p + "ffn_down.weight", cols=(f0, f1))
+            lw.w_down = mat(p + "ffn_down.weight", cols=(f0, f1), scale=cfg.residual_scale)
         elif cfg.is_moe:
             lw.router = f32(p + "ffn_gate_inp.weight")
             for e in range(cfg.n_expert):
@@ -230,14 +236,14 @@ def load_weights(src: str | GGUFModelFiles, device, layer_range: range | None = 
         else:
             lw.w_gate = mat(p + "ffn_gate.weight", rows=(f0, f1))
             lw.w_up = mat(p + "ffn_up.weight", rows=(f0, f1))
-            lw.w_down = mat(p + "ffn_down.weight", cols=(f0, f1))
+            lw.w_down = mat(p + "ffn_down.weight", cols=(f0, f1), scale=cfg.residual_scale)
         layers[il] = lw
 
     tok = mat("token_embd.weight") if first_stage else None
     out_norm = lm = None
     v0, v1 = 0, cfg.vocab_size
     if last_stage:
-        out_norm = f32("output_norm.weight")
+        out_norm = f32("output_norm.weight") / cfg.logit_scale      # granite: logits / logit_scale, folded into the final norm
         name = "output.weight" if "output.weight" in f else "token_embd.weight"
         if shard_vocab and tp_size > 1 and cfg.vocab_size % (2 * tp_size) == 0:
             v0, v1 = _split(cfg.vocab_size, tp_size, tp_rank)

@@ -39,6 +39,35 @@ def slice_raw(raw: np.ndarray, ggml_type: GGMLType, shape: tuple[int, int], rows
     return raw, (N, K)
 
 
+def scale_raw(raw: np.ndarray, ggml_type: GGMLType, shape: tuple[int, int], s: float) -> tuple[np.ndarray, GGMLType]:
+    """Multiply a weight matrix held as GGUF bytes by a scalar without decoding it: block formats only have their fp16 block scales
+    rewritten (granite's residual multiplier is folded into Wo / W_down this way at load time).  Returns (bytes, type); formats
+    the kernels do not read natively come back as fp16."""
+    t = GGMLType(ggml_type)
+    N, K = shape
+    per, nbytes = BLOCK_GEOMETRY[t]
+    raw = np.ascontiguousarray(raw).reshape(-1)
+
+    def rescale(col0, blk_bytes):
+        b = raw.reshape(-1, blk_bytes).copy()
+        for c in col0:
+            d = b[:, c:c + 2].copy().view("<f2").astype(np.float32) * s
+            b[:, c:c + 2] = d.astype("<f2").view(np.uint8)
+        return b.reshape(-1)
+    if t == GGMLType.Q8_0:
+        return rescale([0], 34), t
+    if t == GGMLType.Q4_K:
+        return rescale([0, 2], 144), t
+    if t == GGMLType.Q5_K:
+        return rescale([0, 2], 176), t
+    if t == GGMLType.Q6_K:
+        return rescale([208], 210), t
+    from ..gguf.quants import quantize
+    dense = dequantize(raw, t, (N, K)) * np.float32(s)
+    out_t = t if t in (GGMLType.F16, GGMLType.BF16, GGMLType.F32) else GGMLType.F16
+    return quantize(dense, out_t), out_t
+
+
 @dataclass
 class DeviceWeight:
     wtype: GGMLType

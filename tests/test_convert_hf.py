@@ -27,6 +27,8 @@ CASES = {
     "qwen2-yarn": ("Qwen2Config", "Qwen2ForCausalLM", {"rope_parameters": {"rope_type": "yarn", "rope_theta": 10000.0, "factor": 4.0,
                                                                              "original_max_position_embeddings": 128}}),
     "qwen3": ("Qwen3Config", "Qwen3ForCausalLM", {"head_dim": 128}),
+    "granite": ("GraniteConfig", "GraniteForCausalLM", {"embedding_multiplier": 12.0, "residual_multiplier": 0.22, "logits_scaling": 8.0,
+                                                        "attention_multiplier": 0.015625}),
     "phi3": ("Phi3Config", "Phi3ForCausalLM", {"num_key_value_heads": 4}),
     "mixtral": ("MixtralConfig", "MixtralForCausalLM", {"intermediate_size": 256, "num_local_experts": 4, "num_experts_per_tok": 2}),
     "qwen3moe": ("Qwen3MoeConfig", "Qwen3MoeForCausalLM", {"head_dim": 64, "moe_intermediate_size": 128, "num_experts": 4,

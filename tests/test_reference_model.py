@@ -62,7 +62,8 @@ def test_rope_modes():
 
 
 @pytest.mark.parametrize("key", [("tiny-qwen2", "F16"), ("tiny-qwen2", "Q8_0"), ("tiny-qwen3", "F16"), ("tiny-phi3", "F16"),
-                                 ("tiny-phi3", "Q8_0"), ("tiny-qwen3moe", "F16")])
+                                 ("tiny-phi3", "Q8_0"), ("tiny-qwen3moe", "F16"), ("tiny-granite", "F16"), ("tiny-granite", "Q8_0"),
+                                 ("tiny-granite", "Q4_K_M")])
 def test_other_architectures_match_oracle_cpu(tmp_models, key):
     """qwen2 (QKV bias), qwen3 (per-head Q/K norm) and phi3 (fused QKV / gate-up tensors), all with half-split RoPE:
     engine (CPU op fallbacks, paged KV) against the fp32 oracle."""
@@ -70,7 +71,7 @@ def test_other_architectures_match_oracle_cpu(tmp_models, key):
     from distributed_llm_pipeline_b200.models.weights import load_weights
     path = tmp_models[key]
     ref = ReferenceModel.from_gguf(path)
-    assert ref.cfg.arch == key[0].split("-")[1] and ref.cfg.rope_neox
+    assert ref.cfg.arch == key[0].split("-")[1] and ref.cfg.rope_neox == (ref.cfg.arch != "granite")
     prompt = list(range(5, 22))
     toks, ref_logits = ref.generate_greedy(prompt, 4)
     eng = LlamaEngine(load_weights(path, "cpu"), n_ctx=64, max_seqs=2, page_size=16, max_batch_tokens=32)

@@ -4,7 +4,8 @@
 Parity: `llama.cpp/convert_hf_to_gguf.py` for the architecture families this engine runs: LlamaForCausalLM / MistralForCausalLM
 / MixtralForCausalLM (arch `llama`, Q/K rows permuted from the HF half-split layout to ggml's adjacent-pair rotation; experts
 stacked into `ffn_*_exps`), Qwen2ForCausalLM (`qwen2`, biases), Qwen3ForCausalLM / Qwen3MoeForCausalLM (`qwen3`, `qwen3moe`,
-per-head Q/K norms), Phi3ForCausalLM (`phi3`, fused qkv / gate_up kept fused).
+per-head Q/K norms), Phi3ForCausalLM (`phi3`, fused qkv / gate_up kept fused), GraniteForCausalLM (`granite`: llama tensors plus the
+embedding / residual / attention / logit multipliers).
 Tokenizer: `tokenizer.json` (byte-level BPE -> `gpt2` model with merges) or `tokenizer.model` (SentencePiece -> `llama` model)
 when present, else a synthetic vocabulary (random-init test checkpoints).  Output types: F32 / F16 / BF16 / Q8_0.
 """
@@ -22,7 +23,7 @@ from distributed_llm_pipeline_b200.gguf.constants import FTYPE, TokenType, Value
 from distributed_llm_pipeline_b200.gguf.synth import synthetic_vocab  # noqa: E402
 
 ARCHS = {"LlamaForCausalLM": "llama", "MistralForCausalLM": "llama", "MixtralForCausalLM": "llama", "Qwen2ForCausalLM": "qwen2",
-         "Qwen3ForCausalLM": "qwen3", "Qwen3MoeForCausalLM": "qwen3moe", "Phi3ForCausalLM": "phi3"}
+         "Qwen3ForCausalLM": "qwen3", "Qwen3MoeForCausalLM": "qwen3moe", "Phi3ForCausalLM": "phi3", "GraniteForCausalLM": "granite"}
 LAYER_MAP = {
     "input_layernorm.weight": "attn_norm.weight", "post_attention_layernorm.weight": "ffn_norm.weight",
     "self_attn.q_proj.weight": "attn_q.weight", "self_attn.k_proj.weight": "attn_k.weight", "self_attn.v_proj.weight": "attn_v.weight",
@@ -131,6 +132,11 @@ def convert(src: str, dst: str, outtype: str = "F16") -> str:
     w.add(f"{a}.embedding_length", E, ValueType.UINT32)
     w.add(f"{a}.block_count", L, ValueType.UINT32)
     w.add(f"{a}.feed_forward_length", cfg["intermediate_size"], ValueType.UINT32)
+    if a == "granite":
+        w.add(f"{a}.embedding_scale", float(cfg.get("embedding_multiplier", 1.0)), ValueType.FLOAT32)
+        w.add(f"{a}.residual_scale", float(cfg.get("residual_multiplier", 1.0)), ValueType.FLOAT32)
+        w.add(f"{a}.logit_scale", float(cfg.get("logits_scaling", 1.0)), ValueType.FLOAT32)
+        w.add(f"{a}.attention.scale", float(cfg.get("attention_multiplier", 1.0)), ValueType.FLOAT32)
     n_exp = int(cfg.get("num_local_experts") or cfg.get("num_experts") or 0)
     if n_exp:
         w.add(f"{a}.expert_count", n_exp, ValueType.UINT32)
@@ -217,9 +223,9 @@ def convert(src: str, dst: str, outtype: str = "F16") -> str:
         if name == "lm_head.weight" and cfg.get("tie_word_embeddings"):
             continue
         t = tensors[name].float().numpy()
-        if a == "llama" and out.endswith("attn_q.weight"):
+        if a in ("llama", "granite") and out.endswith("attn_q.weight"):
             t = permute_qk(t, H)
-        if a == "llama" and out.endswith("attn_k.weight"):
+        if a in ("llama", "granite") and out.endswith("attn_k.weight"):
             t = permute_qk(t, Hkv)
         ttype = qtype if t.ndim >= 2 and not out.endswith("_norm.weight") and not out.endswith("ffn_gate_inp.weight") else GGMLType.F32
         if ttype == GGMLType.Q8_0 and t.shape[-1] % 32:
