@@ -399,7 +399,8 @@ class Orchestrator:
         n_predict = int(d.get("n_predict", d.get("max_tokens", self.n_predict)))
         req = Request(prompt=d.get("prompt", ""), n_predict=n_predict if n_predict > 0 else self.sched.eng.n_ctx,
                       sampling=self._sampling_from(d), stop=stop, cache_prompt=bool(d.get("cache_prompt", True)),
-                      ignore_eos=bool(d.get("ignore_eos", False)))
+                      ignore_eos=bool(d.get("ignore_eos", False)), n_keep=int(d.get("n_keep", 0)),
+                      n_draft=int(d.get("speculative.n_max", d.get("n_draft", 0)) or 0))
         rid = "cmpl-" + uuid.uuid4().hex[:24]
         if d.get("stream"):
             writer.write(self._head("200 OK", [("content-type", "text/event-stream"), ("cache-control", "no-cache")] + CORS + [("connection", "close")]))

@@ -40,6 +40,7 @@ class Request:
     ignore_eos: bool = False
     cache_prompt: bool = True
     n_keep: int = 0             # tokens of the prompt that survive a context shift (-1 = the whole prompt)
+    n_draft: int = 0            # > 0: speculative decoding with prompt-lookup drafts of up to this many tokens (greedy requests)
     id: int = 0
     # filled in by the scheduler
     prompt_ids: list[int] = field(default_factory=list)
@@ -277,6 +278,10 @@ class Scheduler:
                 if s.req.cancelled:
                     self._finish(s, "cancelled")
                     gen.remove(s)
+            for s in list(gen):          # speculative slots: draft from the sequence's own history, verify in one forward
+                if self._speculate(s):
+                    gen.remove(s)
+            gen = [s for s in gen if s.state == SlotState.GENERATING]
             if gen:
                 t0 = time.time()
                 sids = [s.sid for s in gen]
@@ -304,6 +309,46 @@ class Scheduler:
                     s.cache_tokens.append(s.next_token)
                     s.n_past += 1
                     self._accept(s, int(t))
+        return True
+
+    def _speculate(self, s: Slot) -> bool:
+        """Draft-and-verify step for one slot (`server-context.cpp` speculative path with the n-gram "lookup" drafter of
+        `common/ngram-cache.cpp`): the pending token plus up to n_draft drafted tokens go through ONE forward that returns logits
+        for every position; the longest prefix the model agrees with is accepted.  Returns False when the slot should take the
+        normal batched decode step instead (no draft found, sampling is not greedy, engine cannot return all logits)."""
+        req = s.req
+        if req.n_draft <= 0 or not req.sampling.greedy or req.sampling.host_only or not hasattr(self.eng, "copy_seq"):
+            return False
+        from .speculative import NgramDrafter
+        history = s.cache_tokens + [s.next_token]
+        room = min(req.n_draft, req.n_predict - len(req.output_ids), self.eng.n_ctx - len(history) - 2, self.eng.max_tokens - 1)
+        draft = NgramDrafter().draft(history, room) if room > 0 else []
+        if not draft:
+            return False
+        t0 = time.time()
+        block = [s.next_token] + draft
+        try:
+            pred = self.eng.prefill(s.sid, block, all_logits=True).argmax(-1).tolist()
+        except (RuntimeError, NotImplementedError):
+            return False
+        n_ok = 0
+        while n_ok < len(draft) and pred[n_ok] == draft[n_ok]:
+            n_ok += 1
+        self.eng.truncate_seq(s.sid, len(history) + n_ok)              # drop the rejected tail of the block from the cache
+        self.metrics.add(n_decode_total=1, n_busy_slots_total=1, tokens_predicted_total=n_ok + 1, tokens_predicted_seconds_total=time.time() - t0,
+                         draft_tokens_total=len(draft), draft_tokens_accepted_total=n_ok)
+        s.cache_tokens.append(s.next_token)                            # the pending token is in the cache now
+        s.n_past += 1
+        for t in draft[:n_ok]:                                         # accepted drafts: emitted, and already cached
+            self._accept(s, int(t))
+            if s.state != SlotState.GENERATING:
+                break
+            s.cache_tokens.append(int(t))
+            s.n_past += 1
+        else:
+            self._accept(s, int(pred[n_ok]))                           # the model's own next token becomes the pending one
+        if s.sid is not None and self.eng.seq_len(s.sid) != len(s.cache_tokens):
+            self.eng.truncate_seq(s.sid, len(s.cache_tokens))          # finished inside the block: cache mirrors cache_tokens again
         return True
 
     def _device_samplable(self, s: Slot) -> bool:

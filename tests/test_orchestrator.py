@@ -304,3 +304,30 @@ def test_ollama_and_anthropic_dialects(server):
                                                                    "messages": [{"role": "user", "content": "hello"}]}).encode())
     text = body.decode()
     assert "event: message_start" in text and "event: content_block_delta" in text and text.rstrip().endswith('{"type": "message_stop"}')
+
+
+def test_scheduler_speculative_lookup_matches_plain_greedy(tmp_models):
+    """n_draft > 0: prompt-lookup drafts verified in one forward inside the serving loop - same text, fewer model passes."""
+    sched, _, _ = build_service(tmp_models[("tiny", "F16")], device="cpu", n_ctx=256, n_slots=2, n_batch=64)
+    prompt = "ka ri to ka ri to ka ri to ka ri"
+    plain = sched.generate(prompt, n_predict=40, sampling=SamplingParams(temperature=0.0), cache_prompt=False, ignore_eos=True)
+    n_dec_plain = sched.metrics.c["n_decode_total"]
+    spec = sched.generate(prompt, n_predict=40, sampling=SamplingParams(temperature=0.0), cache_prompt=False, ignore_eos=True, n_draft=8)
+    assert spec.output_ids == plain.output_ids and spec.text == plain.text and len(spec.output_ids) == 40
+    n_dec_spec = sched.metrics.c["n_decode_total"] - n_dec_plain
+    assert sched.metrics.c.get("draft_tokens_accepted_total", 0) > 0 and n_dec_spec < n_dec_plain
+    # the cache stayed consistent: the same prompt again continues identically
+    again = sched.generate(prompt, n_predict=12, sampling=SamplingParams(temperature=0.0), ignore_eos=True, n_draft=4)
+    assert again.output_ids == plain.output_ids[:12]
+    # two concurrent requests, one speculative and one sampled, share the loop
+    import threading
+    out = {}
+    ts = [threading.Thread(target=lambda: out.__setitem__("a", sched.generate(prompt, n_predict=16, sampling=SamplingParams(temperature=0.0), ignore_eos=True, n_draft=6))),
+          threading.Thread(target=lambda: out.__setitem__("b", sched.generate("x y z", n_predict=16, sampling=SamplingParams(temperature=0.9, seed=3), ignore_eos=True)))]
+    sched.start()
+    for t in ts:
+        t.start()
+    for t in ts:
+        t.join()
+    sched.stop()
+    assert out["a"].output_ids == plain.output_ids[:16] and len(out["b"].output_ids) == 16

@@ -87,7 +87,7 @@ def main(argv=None):
 
     history, last_prompt, last_reply = "", prompt, ""
     while True:
-        req = sched.generate(prompt, n_predict=a.predict, sampling=sampling_from_args(a), ignore_eos=a.ignore_eos, on_event=on_event, n_keep=a.keep)
+        req = sched.generate(prompt, n_predict=a.predict, sampling=sampling_from_args(a), ignore_eos=a.ignore_eos, on_event=on_event, n_keep=a.keep)   # (--lookup / -md take the stand-alone speculative path above)
         sys.stdout.write("\n")
         if not history:
             history = prompt
