@@ -18,6 +18,14 @@ SANITIZERS = {"address": ["-fsanitize=address,undefined", "-fno-omit-frame-point
               "thread": ["-fsanitize=thread", "-fno-omit-frame-pointer", "-g", "-O1"]}
 
 
+# dlp-run links the CUDA runtime and the in-tree kernel library (found next to it through an rpath): built when both exist
+CUDA_HOME = os.environ.get("CUDA_HOME", "/usr/local/cuda")
+OPS_DIR = os.path.normpath(os.path.join(HERE, "..", "ops"))
+if os.path.exists(os.path.join(CUDA_HOME, "include", "cuda_runtime.h")) and os.path.exists(os.path.join(OPS_DIR, "libdlp_b200.so")):
+    TARGETS["dlp-run"] = (["engine.cpp"], ["-pthread", "-mavx2", "-mf16c", f"-I{CUDA_HOME}/include", f"-L{CUDA_HOME}/lib64", f"-L{OPS_DIR}",
+                                           "-Wl,-rpath," + OPS_DIR, "-Wl,-rpath," + f"{CUDA_HOME}/lib64", "-ldlp_b200", "-lcudart"])
+
+
 def path(name: str, sanitize: str | None = None) -> str:
     return os.path.join(BIN, sanitize, name) if sanitize else os.path.join(BIN, name)
 
@@ -37,7 +45,8 @@ def build(force: bool = False, sanitize: str | None = None) -> dict[str, str]:
             out[name] = dst
             continue
         opt = SANITIZERS[sanitize] if sanitize else ["-O3"]
-        cmd = ["g++", "-std=c++17", "-Wall", "-Wno-unused-function"] + opt + flags + src_paths + ["-o", dst]
+        libs = [f for f in flags if f.startswith("-l")]
+        cmd = ["g++", "-std=c++17", "-Wall", "-Wno-unused-function"] + opt + [f for f in flags if not f.startswith("-l")] + src_paths + ["-o", dst] + libs
         res = subprocess.run(cmd, capture_output=True, text=True)
         if res.returncode != 0:
             raise RuntimeError(f"building {name} failed:\n{res.stderr}")
