@@ -21,9 +21,13 @@ SANITIZERS = {"address": ["-fsanitize=address,undefined", "-fno-omit-frame-point
 # dlp-run links the CUDA runtime and the in-tree kernel library (found next to it through an rpath): built when both exist
 CUDA_HOME = os.environ.get("CUDA_HOME", "/usr/local/cuda")
 OPS_DIR = os.path.normpath(os.path.join(HERE, "..", "ops"))
-if os.path.exists(os.path.join(CUDA_HOME, "include", "cuda_runtime.h")) and os.path.exists(os.path.join(OPS_DIR, "libdlp_b200.so")):
-    TARGETS["dlp-run"] = (["engine.cpp"], ["-pthread", "-mavx2", "-mf16c", f"-I{CUDA_HOME}/include", f"-L{CUDA_HOME}/lib64", f"-L{OPS_DIR}",
-                                           "-Wl,-rpath," + OPS_DIR, "-Wl,-rpath," + f"{CUDA_HOME}/lib64", "-ldlp_b200", "-lcudart"])
+
+
+def _refresh_targets():
+    """(evaluated at build time, not import time: the kernel library may be built after this module was imported)"""
+    if os.path.exists(os.path.join(CUDA_HOME, "include", "cuda_runtime.h")) and os.path.exists(os.path.join(OPS_DIR, "libdlp_b200.so")):
+        TARGETS["dlp-run"] = (["engine.cpp"], ["-pthread", "-mavx2", "-mf16c", f"-I{CUDA_HOME}/include", f"-L{CUDA_HOME}/lib64", f"-L{OPS_DIR}",
+                                               "-Wl,-rpath," + OPS_DIR, "-Wl,-rpath," + f"{CUDA_HOME}/lib64", "-ldlp_b200", "-lcudart"])
 
 
 def path(name: str, sanitize: str | None = None) -> str:
@@ -34,6 +38,7 @@ def build(force: bool = False, sanitize: str | None = None) -> dict[str, str]:
     if sanitize and sanitize not in SANITIZERS:
         raise ValueError(f"unknown sanitizer {sanitize!r}; known: {sorted(SANITIZERS)}")
     os.makedirs(os.path.join(BIN, sanitize) if sanitize else BIN, exist_ok=True)
+    _refresh_targets()
     out = {}
     for name, (srcs, flags) in TARGETS.items():
         src_paths = [os.path.join(HERE, s) for s in srcs]
