@@ -54,3 +54,16 @@ def test_pp2_self_feeding_decode_rounds(tmp_models):
            "--master-port", "29641", script, tmp_models[("tiny", "F16")]]
     r = subprocess.run(cmd, capture_output=True, text=True, timeout=300, env=dict(os.environ, OMP_NUM_THREADS="2", CUDA_VISIBLE_DEVICES=""))
     assert r.returncode == 0 and "FEEDBACK_OK" in r.stdout, r.stdout[-2000:] + r.stderr[-2000:]
+
+
+def test_tp4_gloo_with_replicated_kv_heads(tmp_models):
+    """tp = 4 > n_head_kv = 2: KV heads are replicated across rank pairs, Q heads / FFN / vocab split four ways."""
+    r = _torchrun(4, ["--model", tmp_models[("tiny128", "F16")], "--device", "cpu", "--batch", "2", "--tol", "1e-5"], 29651)
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
+    assert "MP_RESULT" in r.stdout
+
+
+def test_pp2_x_tp2_grid_gloo(tmp_models):
+    """The explicit pp x tp grid (2 stages x 2 tensor-parallel ranks, world size 4) the reference cannot express."""
+    r = _torchrun(4, ["--model", tmp_models[("tiny128", "F16")], "--device", "cpu", "--pp", "2", "--batch", "2", "--tol", "1e-5"], 29661)
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
