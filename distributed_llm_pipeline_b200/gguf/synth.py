@@ -29,6 +29,7 @@ def use_more_bits(i_layer: int, n_layer: int) -> bool:
 def tensor_type_for(name: str, ftype: str, i_layer: int, cfg: ModelConfig) -> GGMLType:
     """Per-tensor storage type for a given file type."""
     if name.endswith("_norm.weight") or name == "rope_freqs.weight" or name.endswith("ffn_gate_inp.weight") \
+            or name.endswith("ffn_gate_inp_shexp.weight") \
             or name.endswith(".bias"):
         return GGMLType.F32
     if ftype == "F32":
@@ -136,6 +137,11 @@ def _tensor_plan(cfg: ModelConfig, rope_freqs: bool):
                 (p + "ffn_down_exps.weight", (cfg.n_expert, E, F), il, 0.02),
                 (p + "ffn_up_exps.weight", (cfg.n_expert, F, E), il, 0.02),
             ]
+            if cfg.n_ff_shared:     # qwen2moe shared expert + its scalar gate
+                Fs = cfg.n_ff_shared
+                plan += [(p + "ffn_gate_inp_shexp.weight", (E,), il, 0.0),
+                         (p + "ffn_gate_shexp.weight", (Fs, E), il, 0.02), (p + "ffn_up_shexp.weight", (Fs, E), il, 0.02),
+                         (p + "ffn_down_shexp.weight", (E, Fs), il, 0.02)]
         else:
             plan += [
                 (p + "ffn_gate.weight", (F, E), il, 0.02),
@@ -193,6 +199,8 @@ def write_synthetic_gguf(path: str, cfg: ModelConfig, ftype: str = "F16", seed: 
             w.add(f"{a}.expert_feed_forward_length", cfg.n_ff, ValueType.UINT32)
         w.add(f"{a}.expert_count", cfg.n_expert, ValueType.UINT32)
         w.add(f"{a}.expert_used_count", cfg.n_expert_used, ValueType.UINT32)
+        if cfg.n_ff_shared:
+            w.add(f"{a}.expert_shared_feed_forward_length", cfg.n_ff_shared, ValueType.UINT32)
     if vocab:
         toks, scores, types = synthetic_vocab(cfg.vocab_size)
         w.add("tokenizer.ggml.model", "llama")

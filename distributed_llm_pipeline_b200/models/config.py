@@ -47,6 +47,9 @@ class ModelConfig:
     residual_scale: float = 1.0    # h += residual_scale * block(h)
     logit_scale: float = 1.0       # logits /= logit_scale
     attention_scale: float = 0.0   # replaces 1/sqrt(head_dim) when > 0
+    # qwen2moe: routed experts without re-normalised top-k weights plus an always-on shared expert behind a sigmoid gate
+    moe_norm_topk: bool = True     # renormalise the selected experts' weights (Mixtral, qwen3moe); qwen2moe: False
+    n_ff_shared: int = 0           # > 0: shared-expert FFN width (`ffn_*_shexp`, gate vector `ffn_gate_inp_shexp`)
 
     @property
     def n_gqa(self) -> int:
@@ -90,6 +93,9 @@ PRESETS: dict[str, ModelConfig] = {
     "tiny-qwen3": ModelConfig(name="tiny-qwen3", arch="qwen3", vocab_size=512, n_embd=256, n_layer=2, n_head=4, n_head_kv=2,
                               head_dim=128, n_ff=512, n_ctx_train=512, rope_theta=10000.0, rope_dim=128, rope_neox=True,
                               qk_norm=True),
+    "tiny-qwen2moe": ModelConfig(name="tiny-qwen2moe", arch="qwen2moe", vocab_size=512, n_embd=256, n_layer=2, n_head=4, n_head_kv=2,
+                                 head_dim=64, n_ff=256, n_ctx_train=512, rope_theta=10000.0, rope_dim=64, rope_neox=True, qkv_bias=True,
+                                 n_expert=4, n_expert_used=2, moe_norm_topk=False, n_ff_shared=512),
     "tiny-qwen3moe": ModelConfig(name="tiny-qwen3moe", arch="qwen3moe", vocab_size=512, n_embd=256, n_layer=2, n_head=4, n_head_kv=2,
                                  head_dim=64, n_ff=256, n_ctx_train=512, rope_theta=10000.0, rope_dim=64, rope_neox=True, qk_norm=True,
                                  n_expert=4, n_expert_used=2),
@@ -135,7 +141,7 @@ PRESETS: dict[str, ModelConfig] = {
 # qwen2 adds Q/K/V biases, qwen3 per-head Q/K RMSNorm (qwen3moe: the same attention with Mixtral-style routed experts of
 # `expert_feed_forward_length`), phi3 fused QKV / gate-up tensors; all but llama rotate half-split
 # ("neox") pairs (`llama.cpp/src/llama-model.cpp` llama_model_rope_type).
-SUPPORTED_ARCHS = {"llama", "qwen2", "qwen3", "qwen3moe", "phi3", "granite"}
+SUPPORTED_ARCHS = {"llama", "qwen2", "qwen2moe", "qwen3", "qwen3moe", "phi3", "granite"}
 
 
 def preset(name: str, **overrides) -> ModelConfig:
@@ -185,7 +191,8 @@ def config_from_gguf(meta: dict[str, Any], tensors: dict | None = None) -> Model
         rope_dim=int(g("rope.dimension_count", head_dim)), rope_neox=arch not in ("llama", "granite"), rope_scale_linear=scale,
         embedding_scale=float(g("embedding_scale", 1.0) or 1.0), residual_scale=float(g("residual_scale", 1.0) or 1.0),
         logit_scale=float(g("logit_scale", 1.0) or 1.0), attention_scale=float(g("attention.scale", 0.0) or 0.0),
-        qkv_bias=arch == "qwen2" or (tensors is not None and "blk.0.attn_q.bias" in tensors),
+        moe_norm_topk=arch != "qwen2moe", n_ff_shared=int(g("expert_shared_feed_forward_length", 0) or 0),
+        qkv_bias=arch in ("qwen2", "qwen2moe") or (tensors is not None and "blk.0.attn_q.bias" in tensors),
         qk_norm=arch in ("qwen3", "qwen3moe") or (tensors is not None and "blk.0.attn_q_norm.weight" in tensors),
         fused_qkv=arch == "phi3" or (tensors is not None and "blk.0.attn_qkv.weight" in tensors),
         n_expert=int(g("expert_count", 0) or 0), n_expert_used=int(g("expert_used_count", 0) or 0),

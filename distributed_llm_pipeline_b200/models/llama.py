@@ -338,15 +338,20 @@ class LlamaEngine:
         cfg, comm = self.cfg, self.comm
         h = self.h[:T]
         if (T <= 4 and lw.e_gate_s is not None and cfg.n_expert <= 32 and cfg.n_embd % 256 == 0 and comm.tp_size == 1
-                and lw.router_w.N % 2 == 0):
+                and lw.router_w.N % 2 == 0 and cfg.moe_norm_topk and not cfg.n_ff_shared):
             return self._moe_device(lw, T)
         if xn is None:
             xn = ops.rmsnorm(h, lw.ffn_norm, cfg.rms_eps, out=self.xn[:T])
         logits = xn.float() @ lw.router.T
         probs = torch.softmax(logits, -1)
         topw, topi = probs.topk(cfg.n_expert_used, -1)
-        topw = topw / topw.sum(-1, keepdim=True)
+        if cfg.moe_norm_topk:
+            topw = topw / topw.sum(-1, keepdim=True)
         out = torch.zeros(T, self.E, dtype=torch.float32, device=h.device)
+        if lw.shared_gate is not None:   # qwen2moe: always-on shared expert behind a sigmoid gate (partial sums under TP: the
+            act = ops.linear(lw.w_gate, xn, "swiglu", w_up=lw.w_up, scratch=self._scratch_for(lw.w_gate, lw.w_up))   # gate is replicated)
+            ys = ops.linear(lw.w_down, act, "f32", scratch=self._scratch_for(lw.w_down))
+            out += torch.sigmoid(xn.float() @ lw.shared_gate)[:, None] * ys
         topi_h = topi.cpu()
         for e in torch.unique(topi_h).tolist():
             rows = (topi_h == e).any(-1).nonzero().flatten().to(h.device)
@@ -660,6 +665,7 @@ class LlamaEngine:
         if hidden_in is not None:
             self.h[:B].copy_(hidden_in)
         moe_host = self.cfg.is_moe and not (B <= 4 and self.comm.tp_size == 1 and self.cfg.n_expert <= 32 and
+                                            self.cfg.moe_norm_topk and not self.cfg.n_ff_shared and
                                             next(iter(self.w.layers.values())).e_gate_s is not None)
         graphable = (use_graph and self.eval_callback is None and self.device.type == "cuda" and not moe_host
                      and not getattr(self.comm, "no_graph", False)

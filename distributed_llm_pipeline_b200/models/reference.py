@@ -150,8 +150,14 @@ class ReferenceModel:
         logits = x @ w[p + "ffn_gate_inp.weight"].T
         probs = torch.softmax(logits, dim=-1)
         topw, topi = probs.topk(c.n_expert_used, dim=-1)
-        topw = topw / topw.sum(-1, keepdim=True)
+        if c.moe_norm_topk:
+            topw = topw / topw.sum(-1, keepdim=True)
         out = torch.zeros_like(x)
+        if c.n_ff_shared:   # qwen2moe: shared expert, scaled by sigmoid(x . gate_vector)  (llama.cpp/src/models/qwen2moe.cpp)
+            g = x @ w[p + "ffn_gate_shexp.weight"].T
+            u = x @ w[p + "ffn_up_shexp.weight"].T
+            sh = (torch.nn.functional.silu(g) * u) @ w[p + "ffn_down_shexp.weight"].T
+            out = out + torch.sigmoid(x @ w[p + "ffn_gate_inp_shexp.weight"].reshape(-1, 1)) * sh
         for e in range(c.n_expert):
             sel = (topi == e)
             rows = sel.any(-1).nonzero().flatten()

@@ -35,6 +35,7 @@ class LayerWeights:
     w_down: DeviceWeight | None = None
     # MoE
     router: torch.Tensor | None = None                 # fp32 [n_expert, E]
+    shared_gate: torch.Tensor | None = None            # fp32 [E]: sigmoid gate of the shared expert (qwen2moe; w_gate/w_up/w_down hold it)
     e_gate: list[DeviceWeight] = field(default_factory=list)
     e_up: list[DeviceWeight] = field(default_factory=list)
     e_down: list[DeviceWeight] = field(default_factory=list)
@@ -233,6 +234,12 @@ def load_weights(src: str | GGUFModelFiles, device, layer_range: range | None = 
                 lw.e_up_s, lw.e_up = restack(lw.e_up)
                 lw.e_down_s, lw.e_down = restack(lw.e_down)
                 lw.router_w = DeviceWeight(GGMLType.F16, cfg.n_expert, cfg.n_embd, [lw.router.to(torch.float16).contiguous()])
+            if cfg.n_ff_shared:   # qwen2moe shared expert (split across TP ranks like a dense FFN) + its gate vector
+                s0, s1 = _split(cfg.n_ff_shared, tp_size, tp_rank, 256 if tp_size > 1 else 1)
+                lw.w_gate = mat(p + "ffn_gate_shexp.weight", rows=(s0, s1))
+                lw.w_up = mat(p + "ffn_up_shexp.weight", rows=(s0, s1))
+                lw.w_down = mat(p + "ffn_down_shexp.weight", cols=(s0, s1))
+                lw.shared_gate = f32(p + "ffn_gate_inp_shexp.weight").reshape(-1)
         else:
             lw.w_gate = mat(p + "ffn_gate.weight", rows=(f0, f1))
             lw.w_up = mat(p + "ffn_up.weight", rows=(f0, f1))

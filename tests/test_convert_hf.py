@@ -31,6 +31,9 @@ CASES = {
                                                         "attention_multiplier": 0.015625}),
     "phi3": ("Phi3Config", "Phi3ForCausalLM", {"num_key_value_heads": 4}),
     "mixtral": ("MixtralConfig", "MixtralForCausalLM", {"intermediate_size": 256, "num_local_experts": 4, "num_experts_per_tok": 2}),
+    "qwen2moe": ("Qwen2MoeConfig", "Qwen2MoeForCausalLM", {"moe_intermediate_size": 128, "shared_expert_intermediate_size": 256,
+                                                             "num_experts": 4, "num_experts_per_tok": 2, "norm_topk_prob": False,
+                                                             "decoder_sparse_step": 1, "mlp_only_layers": []}),
     "qwen3moe": ("Qwen3MoeConfig", "Qwen3MoeForCausalLM", {"head_dim": 64, "moe_intermediate_size": 128, "num_experts": 4,
                                                              "num_experts_per_tok": 2, "norm_topk_prob": True}),
 }

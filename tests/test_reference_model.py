@@ -62,7 +62,7 @@ def test_rope_modes():
 
 
 @pytest.mark.parametrize("key", [("tiny-qwen2", "F16"), ("tiny-qwen2", "Q8_0"), ("tiny-qwen3", "F16"), ("tiny-phi3", "F16"),
-                                 ("tiny-phi3", "Q8_0"), ("tiny-qwen3moe", "F16"), ("tiny-granite", "F16"), ("tiny-granite", "Q8_0"),
+                                 ("tiny-phi3", "Q8_0"), ("tiny-qwen3moe", "F16"), ("tiny-qwen2moe", "F16"), ("tiny-granite", "F16"), ("tiny-granite", "Q8_0"),
                                  ("tiny-granite", "Q4_K_M")])
 def test_other_architectures_match_oracle_cpu(tmp_models, key):
     """qwen2 (QKV bias), qwen3 (per-head Q/K norm) and phi3 (fused QKV / gate-up tensors), all with half-split RoPE:

@@ -3,7 +3,7 @@
 
 Parity: `llama.cpp/convert_hf_to_gguf.py` for the architecture families this engine runs: LlamaForCausalLM / MistralForCausalLM
 / MixtralForCausalLM (arch `llama`, Q/K rows permuted from the HF half-split layout to ggml's adjacent-pair rotation; experts
-stacked into `ffn_*_exps`), Qwen2ForCausalLM (`qwen2`, biases), Qwen3ForCausalLM / Qwen3MoeForCausalLM (`qwen3`, `qwen3moe`,
+stacked into `ffn_*_exps`), Qwen2ForCausalLM (`qwen2`, biases), Qwen2MoeForCausalLM (`qwen2moe`: shared expert), Qwen3ForCausalLM / Qwen3MoeForCausalLM (`qwen3`, `qwen3moe`,
 per-head Q/K norms), Phi3ForCausalLM (`phi3`, fused qkv / gate_up kept fused), GraniteForCausalLM (`granite`: llama tensors plus the
 embedding / residual / attention / logit multipliers).
 Tokenizer: `tokenizer.json` (byte-level BPE -> `gpt2` model with merges) or `tokenizer.model` (SentencePiece -> `llama` model)
@@ -23,7 +23,7 @@ from distributed_llm_pipeline_b200.gguf.constants import FTYPE, TokenType, Value
 from distributed_llm_pipeline_b200.gguf.synth import synthetic_vocab  # noqa: E402
 
 ARCHS = {"LlamaForCausalLM": "llama", "MistralForCausalLM": "llama", "MixtralForCausalLM": "llama", "Qwen2ForCausalLM": "qwen2",
-         "Qwen3ForCausalLM": "qwen3", "Qwen3MoeForCausalLM": "qwen3moe", "Phi3ForCausalLM": "phi3", "GraniteForCausalLM": "granite"}
+         "Qwen2MoeForCausalLM": "qwen2moe", "Qwen3ForCausalLM": "qwen3", "Qwen3MoeForCausalLM": "qwen3moe", "Phi3ForCausalLM": "phi3", "GraniteForCausalLM": "granite"}
 LAYER_MAP = {
     "input_layernorm.weight": "attn_norm.weight", "post_attention_layernorm.weight": "ffn_norm.weight",
     "self_attn.q_proj.weight": "attn_q.weight", "self_attn.k_proj.weight": "attn_k.weight", "self_attn.v_proj.weight": "attn_v.weight",
@@ -143,6 +143,8 @@ def convert(src: str, dst: str, outtype: str = "F16") -> str:
         w.add(f"{a}.expert_used_count", int(cfg.get("num_experts_per_tok", 2)), ValueType.UINT32)
         if cfg.get("moe_intermediate_size"):
             w.add(f"{a}.expert_feed_forward_length", int(cfg["moe_intermediate_size"]), ValueType.UINT32)
+        if a == "qwen2moe" and cfg.get("shared_expert_intermediate_size"):
+            w.add(f"{a}.expert_shared_feed_forward_length", int(cfg["shared_expert_intermediate_size"]), ValueType.UINT32)
     w.add(f"{a}.attention.head_count", H, ValueType.UINT32)
     w.add(f"{a}.attention.head_count_kv", Hkv, ValueType.UINT32)
     w.add(f"{a}.attention.layer_norm_rms_epsilon", float(cfg.get("rms_norm_eps", 1e-5)), ValueType.FLOAT32)
@@ -191,7 +193,12 @@ def convert(src: str, dst: str, outtype: str = "F16") -> str:
             continue
         il, rest = m.group(1), m.group(2)
         t = tensors[name]
-        if rest == "gate.weight":
+        if rest.startswith("shared_expert"):
+            sh = {"shared_expert_gate.weight": "ffn_gate_inp_shexp.weight", "shared_expert.gate_proj.weight": "ffn_gate_shexp.weight",
+                  "shared_expert.up_proj.weight": "ffn_up_shexp.weight", "shared_expert.down_proj.weight": "ffn_down_shexp.weight"}[rest]
+            t2 = tensors.pop(name)
+            tensors[f"__moe__.blk.{il}.{sh}"] = t2.reshape(-1) if sh == "ffn_gate_inp_shexp.weight" else t2
+        elif rest == "gate.weight":
             tensors[f"__moe__.blk.{il}.ffn_gate_inp.weight"] = tensors.pop(name)
         elif rest == "experts.gate_up_proj":
             g, u = t.float().chunk(2, dim=1)
@@ -227,7 +234,7 @@ def convert(src: str, dst: str, outtype: str = "F16") -> str:
             t = permute_qk(t, H)
         if a in ("llama", "granite") and out.endswith("attn_k.weight"):
             t = permute_qk(t, Hkv)
-        ttype = qtype if t.ndim >= 2 and not out.endswith("_norm.weight") and not out.endswith("ffn_gate_inp.weight") else GGMLType.F32
+        ttype = qtype if t.ndim >= 2 and not out.endswith("_norm.weight") and not out.endswith("ffn_gate_inp.weight") and not out.endswith("ffn_gate_inp_shexp.weight") else GGMLType.F32
         if ttype == GGMLType.Q8_0 and t.shape[-1] % 32:
             ttype = GGMLType.F16
         arr = np.ascontiguousarray(t)
