@@ -333,6 +333,12 @@ int dlp_sample(const float* logits, int R, int V, int ld, int top_k, float top_p
     DLP_REQUIRE(logits && out, "dlp_sample: null argument");
     return sample(logits, R, V, ld, top_k, top_p, min_p, temp, seed, step_ctr, out, (cudaStream_t)stream);
 }
+int dlp_sample_dev(const float* logits, int R, int V, int ld, dlp_sample_params* params, const int32_t* row_slot, int32_t* out,
+                   void* stream) {
+    DLP_REQUIRE(logits && out && params, "dlp_sample_dev: null argument");
+    static_assert(sizeof(dlp_sample_params) == sizeof(SampleParams), "sampler record layout");
+    return sample_dev(logits, R, V, ld, reinterpret_cast<SampleParams*>(params), row_slot, out, (cudaStream_t)stream);
+}
 int dlp_f32_to_f16(const float* in, void* out, size_t n, void* stream) {
     DLP_REQUIRE(in && out, "dlp_f32_to_f16: null argument");
     return f32_to_f16(in, (__half*)out, n, (cudaStream_t)stream);

@@ -107,7 +107,11 @@ __global__ void __launch_bounds__(256) rs_norm_ag_kernel(const RsNormAg a) {
 int rs_norm_ag(const RsNormAg& a, cudaStream_t s) {
     DLP_REQUIRE(a.h_shard && a.rows > 0 && a.E % 8 == 0 && a.tp >= 1 && a.tp <= 8, "rs_norm_ag: bad descriptor");
     DLP_REQUIRE(a.norm_w == nullptr || a.done != nullptr, "rs_norm_ag: the gather needs a completion counter");
-    rs_norm_ag_kernel<<<a.rows, 256, (size_t)a.E * 4, s>>>(a);
+    const size_t smem = (size_t)a.E * 4;
+    DLP_REQUIRE(smem <= 200 * 1024, "rs_norm_ag: n_embd %d does not fit the row staging buffer", a.E);
+    if (first_use_on_device((const void*)rs_norm_ag_kernel))   // rows wider than 12288 need more than the default 48 KB
+        DLP_CHECK_CUDA(cudaFuncSetAttribute(rs_norm_ag_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+    rs_norm_ag_kernel<<<a.rows, 256, smem, s>>>(a);
     DLP_LAUNCH_CHECK();
     return 0;
 }

@@ -321,12 +321,9 @@ __device__ __forceinline__ uint32_t f2ord(float f) {  // order-preserving float 
     return (u & 0x80000000u) ? ~u : (u | 0x80000000u);
 }
 
-__global__ void __launch_bounds__(1024) argmax_kernel(const float* __restrict__ logits, int V, int ld, int* __restrict__ out) {
+__device__ __forceinline__ void argmax_row(const float* __restrict__ row, int V, int* __restrict__ out_slot) {
     __shared__ float sv[32];
     __shared__ int si[32];
-    const float* row = logits + (size_t)blockIdx.x * ld;
-    pdl_wait();
-    pdl_launch_dependents();
     float best = -INFINITY;
     int bi = 0;
     if ((reinterpret_cast<uintptr_t>(row) & 15) == 0) {
@@ -368,8 +365,14 @@ __global__ void __launch_bounds__(1024) argmax_kernel(const float* __restrict__ 
             const int oi = __shfl_xor_sync(0xffffffffu, bi, o);
             if (ov > best || (ov == best && oi < bi)) { best = ov; bi = oi; }
         }
-        if (lane == 0) out[blockIdx.x] = bi;
+        if (lane == 0) *out_slot = bi;
     }
+}
+
+__global__ void __launch_bounds__(1024) argmax_kernel(const float* __restrict__ logits, int V, int ld, int* __restrict__ out) {
+    pdl_wait();
+    pdl_launch_dependents();
+    argmax_row(logits + (size_t)blockIdx.x * ld, V, out + blockIdx.x);
 }
 
 int argmax(const float* logits, int R, int V, int ld, int* out, cudaStream_t s) {
@@ -381,17 +384,13 @@ int argmax(const float* logits, int R, int V, int ld, int* out, cudaStream_t s) 
 constexpr int SAMPLE_MAX_CAND = 1024;
 
 // top-k -> top-p -> min-p -> temperature -> multinomial draw
-__global__ void __launch_bounds__(1024) sample_kernel(const float* __restrict__ logits, int V, int ld, int top_k, float top_p,
-                                                      float min_p, float temp, uint32_t seed, const int* __restrict__ step_ctr,
-                                                      int* __restrict__ out) {
+__device__ __forceinline__ void sample_row(const float* __restrict__ row, int V, int top_k, float top_p, float min_p, float temp,
+                                           uint32_t seed, uint32_t ctr, int* __restrict__ out_slot) {
     __shared__ int s_count;
     __shared__ uint32_t s_lo, s_hi;
     __shared__ float cv[SAMPLE_MAX_CAND];
     __shared__ int ci[SAMPLE_MAX_CAND];
     __shared__ int s_n;
-    const float* row = logits + (size_t)blockIdx.x * ld;
-    pdl_wait();
-    pdl_launch_dependents();
     const int k = max(1, min(top_k <= 0 ? SAMPLE_MAX_CAND : top_k, min(V, SAMPLE_MAX_CAND)));
     // radix select (4 passes of 8 bits, most significant first) on the order-preserving integer image of the logits:
     // after the passes `prefix` is the key of the k-th largest element
@@ -468,8 +467,7 @@ __global__ void __launch_bounds__(1024) sample_kernel(const float* __restrict__ 
         if (temp > 0.f && n > 1) {
             float z = 0.f;
             for (int a = 0; a < n; ++a) z += __expf((cv[a] - mx) / temp);
-            const uint32_t ctr = step_ctr ? (uint32_t)step_ctr[0] : 0u;
-            const uint32_t r = hash_u32(seed ^ hash_u32(ctr * 0x9E3779B9u + blockIdx.x + 0x85ebca6bu));
+            const uint32_t r = hash_u32(seed ^ hash_u32(ctr + 0x85ebca6bu));
             const float u = (float)(r >> 8) * (1.0f / 16777216.0f) * z;
             float cum = 0.f;
             choice = n - 1;
@@ -478,8 +476,44 @@ __global__ void __launch_bounds__(1024) sample_kernel(const float* __restrict__ 
                 if (u < cum) { choice = a; break; }
             }
         }
-        out[blockIdx.x] = ci[choice];
+        *out_slot = ci[choice];
     }
+}
+
+__global__ void __launch_bounds__(1024) sample_kernel(const float* __restrict__ logits, int V, int ld, int top_k, float top_p,
+                                                      float min_p, float temp, uint32_t seed, const int* __restrict__ step_ctr,
+                                                      int* __restrict__ out) {
+    pdl_wait();
+    pdl_launch_dependents();
+    sample_row(logits + (size_t)blockIdx.x * ld, V, top_k, top_p, min_p, temp, seed,
+               (step_ctr ? (uint32_t)step_ctr[0] : 0u) * 0x9E3779B9u + blockIdx.x, out + blockIdx.x);
+}
+
+// Sampler parameters read from device memory: one record per sequence slot, picked through the batch-row -> slot map the
+// decode step already keeps on the device.  One captured graph therefore serves every request (nothing about a request is
+// baked into the launch), greedy and sampled rows can share a batch, and the random stream is per request: the record's own
+// draw counter starts at zero when the host (re)writes the record and advances here, so the same seed and prompt give the
+// same tokens whatever the server did before.  ref: per-slot `common_sampler` with its own RNG (common/sampling.cpp:179-311).
+__global__ void __launch_bounds__(1024) sample_dev_kernel(const float* __restrict__ logits, int V, int ld, SampleParams* __restrict__ params,
+                                                          const int* __restrict__ row_slot, int* __restrict__ out) {
+    pdl_wait();
+    pdl_launch_dependents();
+    SampleParams* pp = params + (row_slot ? row_slot[blockIdx.x] : (int)blockIdx.x);
+    const SampleParams p = *pp;
+    const float* row = logits + (size_t)blockIdx.x * ld;
+    if (p.temp <= 0.f) {
+        argmax_row(row, V, out + blockIdx.x);
+        return;
+    }
+    __syncthreads();   // every thread holds its copy of the record before thread 0 advances the counter
+    if (threadIdx.x == 0) pp->ctr = p.ctr + 1;
+    sample_row(row, V, p.top_k, p.top_p, p.min_p, p.temp, p.seed, p.ctr * 0x9E3779B9u, out + blockIdx.x);
+}
+
+int sample_dev(const float* logits, int R, int V, int ld, SampleParams* params, const int* row_slot, int* out, cudaStream_t s) {
+    DLP_REQUIRE(R > 0 && V > 0 && params != nullptr, "sample_dev: bad argument");
+    DLP_CHECK_CUDA(launch_pdl(sample_dev_kernel, dim3(R), dim3(1024), 0, s, logits, V, ld, params, row_slot, out));
+    return 0;
 }
 
 int sample(const float* logits, int R, int V, int ld, int top_k, float top_p, float min_p, float temp, uint32_t seed,

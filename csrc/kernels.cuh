@@ -110,6 +110,15 @@ int advance(int* seq_len, const int* active, int* pos, int* slot, int* kv_len, c
 int argmax(const float* logits, int R, int V, int ld, int* out, cudaStream_t s);
 int sample(const float* logits, int R, int V, int ld, int top_k, float top_p, float min_p, float temp, uint32_t seed,
            const int* step_ctr, int* out, cudaStream_t s);
+// per-sequence sampler record in device memory (32 bytes; mirrors dlp_sample_params in include/dlp_b200.h)
+struct SampleParams {
+    int top_k;
+    float top_p, min_p, temp;
+    uint32_t seed;
+    uint32_t ctr;       // draws made with this record so far (advanced by the kernel)
+    uint32_t pad[2];
+};
+int sample_dev(const float* logits, int R, int V, int ld, SampleParams* params, const int* row_slot, int* out, cudaStream_t s);
 int f32_to_f16(const float* in, __half* out, size_t n, cudaStream_t s);
 int attn_paged(const AttnParams& p, int D, cudaStream_t s);
 int attn_paged_static(AttnParams p, int D, cudaStream_t s);

@@ -140,6 +140,11 @@ class LlamaEngine:
         self.seq_len_dev = torch.zeros(max_seqs, dtype=i32, device=dev)
         self.next_tok = torch.zeros(max_seqs, dtype=i32, device=dev)
         self.step_ctr = torch.zeros(1, dtype=i32, device=dev)
+        # per-sequence sampler records (dlp_sample_params: top_k, top_p, min_p, temp, seed, draw counter) read by the device sampler
+        self.samp = torch.zeros(max_seqs, ops.SAMPLE_REC_WORDS, dtype=i32, device=dev)
+        self._samp_host: dict[int, tuple] = {}      # what each record currently holds
+        self._seq_sampling: dict[int, tuple] = {}   # per-sequence overrides of self.sampling (set_seq_sampling)
+        self.max_graphs = int(os.environ.get("DLP_MAX_GRAPHS", "24"))
         v0, v1 = weights.vocab_range
         self.logits = torch.zeros(max_seqs, v1 - v0, dtype=f32, device=dev) if last_stage else None
         self.attn_splits = attn_splits if attn_splits is not None else (16 if dev.type == "cuda" else 1)
@@ -176,6 +181,23 @@ class LlamaEngine:
     def free_seq(self, sid: int):
         self.kv.release(self.seqs.pop(sid))
         self._free_sids.append(sid)
+        self._seq_sampling.pop(sid, None)
+        self._samp_host.pop(sid, None)
+
+    def set_seq_sampling(self, sid: int, top_k: int = 40, top_p: float = 0.95, min_p: float = 0.05, temp: float = 0.0, seed: int = 0):
+        """Sampler parameters of one sequence for the device sampler; also restarts that sequence's random stream, so a request
+        with a given seed draws the same tokens whatever ran before it (the reference keeps one seeded RNG per slot,
+        `common/sampling.cpp:179-311`).  Sequences without their own record follow `self.sampling`."""
+        self._seq_sampling[sid] = (int(top_k), float(top_p), float(min_p), float(temp), int(seed))
+        self._samp_host.pop(sid, None)
+
+    def _sync_sampling(self, sids):
+        for sid in sids:
+            s = self.sampling
+            want = self._seq_sampling.get(sid) or (s["top_k"], s["top_p"], s["min_p"], s["temp"], s["seed"])
+            if self._samp_host.get(sid) != want:
+                self.samp[sid].copy_(ops.pack_sample_record(*want))
+                self._samp_host[sid] = want
 
     def seq_len(self, sid: int) -> int:
         return self.seqs[sid].length
@@ -642,10 +664,8 @@ class LlamaEngine:
             if not fused and not sp:
                 lg = self._head(slice(0, B), B)
             self.logits_full = lg  # full-vocab logits (gathered across TP ranks); static across graph replays
-            if sample:
-                s = self.sampling
-                ops.sample(lg, s["top_k"], s["top_p"], s["min_p"], s["temp"], s["seed"], self.step_ctr, out=self.next_tok[:B])
-                self.step_ctr.add_(1)
+            if sample:   # records are indexed by sequence slot through the row -> slot map: nothing of a request is baked in
+                ops.sample_dev(lg, self.samp, self.active[:B], self.next_tok[:B])
 
     @torch.no_grad()
     def decode(self, sids: list[int], tokens=None, hidden_in: torch.Tensor | None = None, sample: bool = True,
@@ -671,17 +691,25 @@ class LlamaEngine:
                      and not getattr(self.comm, "no_graph", False)
                      and not (self.fused_tp and B > 4))   # SP path passes host-side epochs as kernel arguments
         self._onepass_now = self.attn_onepass and max(self.seqs[sid].length for sid in sids) + 1 >= self.attn_onepass_min
+        if sample and self.last_stage:
+            self._sync_sampling(sids)
         if graphable:
-            # sampler scalars and the attention variant are baked into the graph
-            key = (B, sample, self._onepass_now) + (tuple(self.sampling.values()) if sample else ())
-            g = self._graphs.get(key)
+            # only the batch size, the output kind and the attention variant shape the graph (sampler parameters are device data)
+            key = (B, sample, self._onepass_now)
+            g = self._graphs.pop(key, None)
             if g is None:
+                while len(self._graphs) + 2 > self.max_graphs:    # least recently used graphs go first
+                    old = next(iter(self._graphs))
+                    del self._graphs[old]
+                    self._graph_launches.pop(old, None)
                 if self.attn_onepass:   # capture the other attention variant now as well: the switch at 64 keys must not stall
                     want = self._onepass_now
                     self._onepass_now = not want
-                    self._capture(B, sample, key[:2] + (not want,) + key[3:])
+                    self._capture(B, sample, key[:2] + (not want,))
                     self._onepass_now = want
                 g = self._capture(B, sample, key)
+                self._graphs.pop(key)
+            self._graphs[key] = g      # most recently used last
             g.replay()
             self.launches_replayed += self._graph_launches.get(key, 0)
         else:
@@ -697,6 +725,8 @@ class LlamaEngine:
         saved = self.seq_len_dev.clone()
         saved_ctr = self.step_ctr.clone()
         saved_h = self.h[:B].clone()   # non-first stages consume their input hidden state in place: the warm-up must not eat it
+        saved_tok = self.next_tok.clone()   # the warm-up samples into next_tok: the pending input token must survive it
+        saved_samp = self.samp.clone()      # ... and advances the draw counters
         s = torch.cuda.Stream()
         s.wait_stream(torch.cuda.current_stream())
         with torch.cuda.stream(s):
@@ -705,6 +735,8 @@ class LlamaEngine:
         self.seq_len_dev.copy_(saved)
         self.step_ctr.copy_(saved_ctr)
         self.h[:B].copy_(saved_h)
+        self.next_tok.copy_(saved_tok)
+        self.samp.copy_(saved_samp)
         g = torch.cuda.CUDAGraph()
         n0 = ops.launch_count
         with torch.cuda.graph(g):
@@ -726,8 +758,12 @@ class LlamaEngine:
             sid = self.alloc_seq()
         logits = self.prefill(sid, prompt)
         s = self.sampling
-        tok = (ops.argmax(logits[None]) if s["temp"] <= 0 else
-               ops.sample(logits[None], s["top_k"], s["top_p"], s["min_p"], s["temp"], s["seed"], self.step_ctr))
+        if s["temp"] <= 0:
+            tok = ops.argmax(logits[None])
+        else:   # first token from the prefill logits: same per-sequence record (and random stream) as the decode steps
+            self._sync_sampling([sid])
+            tok = ops.sample_dev(logits[None], self.samp, torch.tensor([sid], dtype=torch.int32, device=self.device),
+                                 torch.empty(1, dtype=torch.int32, device=self.device))
         self.next_tok[:1].copy_(tok)
         out = [int(tok[0])]
         for _ in range(n_predict - 1):

@@ -6,6 +6,7 @@ library cannot be loaded the call raises.
 """
 from __future__ import annotations
 
+import ctypes as C
 import math
 
 import torch
@@ -364,6 +365,41 @@ def sample(logits: torch.Tensor, top_k: int = 40, top_p: float = 0.95, min_p: fl
         return out
     _lib.check(_lib.load().dlp_sample(logits.data_ptr(), R, V, logits.stride(0), top_k, top_p, min_p, temp, seed & 0xFFFFFFFF,
                                       _p(step_ctr), out.data_ptr(), _stream()), "sample")
+    _count()
+    return out
+
+
+SAMPLE_REC_WORDS = 8   # int32 words per dlp_sample_params record: top_k, top_p, min_p, temp, seed, ctr, 2 reserved
+
+
+def pack_sample_record(top_k: int, top_p: float, min_p: float, temp: float, seed: int) -> torch.Tensor:
+    """Host image (int32 [8]) of one dlp_sample_params record with its draw counter at zero."""
+    import struct
+    return torch.tensor(struct.unpack("8i", struct.pack("ifffII2I", int(top_k), float(top_p), float(min_p), float(temp),
+                                                        seed & 0xFFFFFFFF, 0, 0, 0)), dtype=torch.int32)
+
+
+def sample_dev(logits: torch.Tensor, params: torch.Tensor, row_slot: torch.Tensor | None, out: torch.Tensor) -> torch.Tensor:
+    """Sampler chain with per-sequence records in device memory (`params` int32 [n_slots, 8]; row i uses record row_slot[i]).
+    Nothing request-specific is a launch argument, so one captured graph serves every request."""
+    R, V = logits.shape
+    if not native(logits):
+        import struct
+        from ..serving.sampler import sample_reference
+        for i in range(R):
+            slot = int(row_slot[i]) if row_slot is not None else i
+            k, tp, mp, t, seed, ctr, _, _ = struct.unpack("ifffII2I", params[slot].cpu().numpy().tobytes())
+            if t <= 0:
+                out[i] = int(logits[i].argmax())
+            else:
+                out[i:i + 1].copy_(sample_reference(logits[i:i + 1], k, tp, mp, t, seed + ctr))
+                params[slot, 5] += 1
+        return out
+    lib = _lib.load()
+    lib.dlp_sample_dev.restype = C.c_int
+    lib.dlp_sample_dev.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
+    _lib.check(lib.dlp_sample_dev(logits.data_ptr(), R, V, logits.stride(0), params.data_ptr(), _p(row_slot), out.data_ptr(), _stream()),
+               "sample_dev")
     _count()
     return out
 

@@ -16,7 +16,14 @@ import torch.distributed as dist
 
 
 class PipelineStage:
-    def __init__(self, engine, grid, wire_dtype: torch.dtype = torch.float32, max_microbatches: int = 4):
+    WIRE = {"f32": torch.float32, "f16": torch.float16, "bf16": torch.bfloat16}
+
+    def __init__(self, engine, grid, wire_dtype: torch.dtype | None = None, max_microbatches: int = 4):
+        """`wire_dtype`: what crosses the stage boundary.  Default fp16 (half the bytes of the reference's F32 hop,
+        `ggml-cuda.cu:2826`; values beyond the fp16 range are clamped, not turned into inf); env DLP_PP_WIRE=f32|f16|bf16."""
+        import os
+        if wire_dtype is None:
+            wire_dtype = self.WIRE[os.environ.get("DLP_PP_WIRE", "f16")]
         self.eng, self.grid = engine, grid
         self.prev, self.next = grid.pp_prev, grid.pp_next
         self.first, self.last = grid.first_stage, grid.last_stage
@@ -33,6 +40,8 @@ class PipelineStage:
     # ---- helpers ----------------------------------------------------------------------------------
     def _send_hidden(self, h: torch.Tensor, slot: int):
         buf = self.tx[slot][: h.shape[0]]
+        if self.wire_dtype == torch.float16 and h.dtype == torch.float32:
+            h = h.clamp(-65504.0, 65504.0)
         buf.copy_(h)
         return dist.isend(buf, dst=self.next)
 

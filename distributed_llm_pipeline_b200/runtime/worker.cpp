@@ -173,6 +173,7 @@ struct Stage {
     bool first = false, last = false;
     std::vector<float> inv_freq;
     std::map<uint32_t, SeqCache> seqs;
+    int max_seqs = 64;           // --max-seqs: cap on live sequences (each holds an n_ctx KV cache)
 
     void load(const std::string& path, int a, int b, int n_ctx) {
         g.open(path);
@@ -203,6 +204,8 @@ struct Stage {
     SeqCache& seq(uint32_t id) {
         auto it = seqs.find(id);
         if (it != seqs.end()) return it->second;
+        // every live sequence owns a full n_ctx KV cache: an unauthenticated peer must not be able to allocate without bound
+        if (seqs.size() >= (size_t)max_seqs) throw std::runtime_error("too many live sequences (limit " + std::to_string(max_seqs) + "); RESET one first");
         SeqCache& c = seqs[id];
         const size_t kv = (size_t)hp.n_head_kv * hp.head_dim;
         c.k.assign(l1 - l0, std::vector<float>((size_t)hp.n_ctx * kv));
@@ -226,6 +229,7 @@ struct Stage {
     std::vector<float> run(uint32_t sid, int T, int pos0, uint32_t flags, const uint8_t* payload, size_t nbytes) {
         const int E = hp.n_embd, D = hp.head_dim, Hq = hp.n_head, Hkv = hp.n_head_kv, F = hp.n_ff;
         if (T <= 0 || T > hp.n_ctx) throw std::runtime_error("bad token count");
+        if (pos0 < 0 || pos0 > hp.n_ctx - T) throw std::runtime_error("context overflow");   // also rejects wire values >= 2^31
         SeqCache& c = seq(sid);
         if (pos0 != c.len) throw std::runtime_error("position " + std::to_string(pos0) + " does not continue sequence of length " + std::to_string(c.len));
         if (pos0 + T > hp.n_ctx) throw std::runtime_error("context overflow");
@@ -365,7 +369,14 @@ bool serve_client(int fd, Stage& st, bool verbose) {
                     break;
                 }
                 case RESET: st.seqs.erase(seq_id); reply(fd, 0, nullptr, 0); break;
-                case TRUNCATE: { auto it = st.seqs.find(seq_id); if (it != st.seqs.end()) it->second.len = std::min<int>(it->second.len, (int)rq.pos0); reply(fd, 0, nullptr, 0); break; }
+                case TRUNCATE: {
+                    const uint32_t new_len = rq.pos0;   // unsigned on the wire: compare before any narrowing
+                    if (new_len > (uint32_t)st.hp.n_ctx) throw std::runtime_error("TRUNCATE: length beyond the context window");
+                    auto it = st.seqs.find(seq_id);
+                    if (it != st.seqs.end()) it->second.len = std::max(0, std::min<int>(it->second.len, (int)new_len));
+                    reply(fd, 0, nullptr, 0);
+                    break;
+                }
                 case SHUTDOWN: reply(fd, 0, nullptr, 0); return false;
                 default: reply(fd, 5, "unknown command", 15); return true;
             }
@@ -381,7 +392,7 @@ bool serve_client(int fd, Stage& st, bool verbose) {
 int main(int argc, char** argv) {
     signal(SIGPIPE, SIG_IGN);
     std::string model, host = "127.0.0.1";
-    int port = 50052, l0 = 0, l1 = -1, n_ctx = 2048;
+    int port = 50052, l0 = 0, l1 = -1, n_ctx = 2048, max_seqs = 64;
     bool verbose = false;
     for (int i = 1; i < argc; ++i) {
         std::string a = argv[i];
@@ -392,10 +403,12 @@ int main(int argc, char** argv) {
         else if (a == "--layers") { std::string v = next(); size_t c = v.find(':'); l0 = atoi(v.substr(0, c).c_str()); l1 = c == std::string::npos ? -1 : atoi(v.substr(c + 1).c_str()); }
         else if (a == "-c" || a == "--ctx-size") n_ctx = atoi(next().c_str());
         else if (a == "-v" || a == "--verbose") verbose = true;
-        else { fprintf(stderr, "dlp-worker -m model.gguf [--layers a:b] [-H host] [-p port] [-c n_ctx] [-v]\n"); return a == "-h" ? 0 : 2; }
+        else if (a == "--max-seqs") max_seqs = std::max(1, atoi(next().c_str()));
+        else { fprintf(stderr, "dlp-worker -m model.gguf [--layers a:b] [-H host] [-p port] [-c n_ctx] [--max-seqs n] [-v]\n"); return a == "-h" ? 0 : 2; }
     }
     if (model.empty()) { fprintf(stderr, "dlp-worker: -m model.gguf is required\n"); return 2; }
     Stage st;
+    st.max_seqs = max_seqs;
     try { st.load(model, l0, l1, n_ctx); } catch (const std::exception& e) { fprintf(stderr, "dlp-worker: %s\n", e.what()); return 1; }
     if (host != "127.0.0.1" && host != "localhost")
         fprintf(stderr, "WARNING: listening on %s - the worker protocol is unauthenticated; never expose it to an untrusted network\n", host.c_str());

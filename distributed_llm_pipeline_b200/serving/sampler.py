@@ -55,7 +55,8 @@ class SamplingParams:
 
 
 def apply_penalties(logits: torch.Tensor, history: list[int], p: SamplingParams) -> torch.Tensor:
-    if not history or (p.repeat_penalty == 1.0 and p.frequency_penalty == 0.0 and p.presence_penalty == 0.0):
+    # repeat_last_n: 0 disables the penalties, -1 covers the whole history (llama-sampling.cpp:2777 `penalty_last_n`)
+    if not history or p.repeat_last_n == 0 or (p.repeat_penalty == 1.0 and p.frequency_penalty == 0.0 and p.presence_penalty == 0.0):
         return logits
     logits = logits.clone()
     recent = history[-p.repeat_last_n:] if p.repeat_last_n > 0 else history
@@ -220,8 +221,10 @@ class Sampler:
     def sample(self, logits: torch.Tensor) -> int:
         p = self.p
         row = logits.float().cpu()
-        for tid, bias in p.logit_bias.items():
-            row[tid] += bias
+        if p.logit_bias:
+            row = row.clone()        # an fp32 CPU input comes back as the caller's own tensor: never write into it
+            for tid, bias in p.logit_bias.items():
+                row[tid] += bias
         row = apply_penalties(row, self.history, p)
         row = apply_dry(row, self.history, p)
         tok = self._pick(row)

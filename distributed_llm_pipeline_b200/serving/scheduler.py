@@ -202,6 +202,9 @@ class Scheduler:
         slot.n_past = keep
         slot.req, slot.state = req, SlotState.PROMPT
         slot.sampler = Sampler(req.sampling, self.tok)
+        if hasattr(eng, "set_seq_sampling"):    # the device sampler's record of this sequence; restarts its random stream
+            p = req.sampling
+            eng.set_seq_sampling(slot.sid, p.top_k, p.top_p, p.min_p, p.temperature, p.seed)
         slot.decoder = StreamDecoder(self.tok)
         req.n_prompt_cached = keep
         req.t_start = time.time()
@@ -287,10 +290,9 @@ class Scheduler:
                 sids = [s.sid for s in gen]
                 toks = torch.tensor([s.next_token for s in gen], dtype=torch.int32)
                 try:
-                    device_sampling = all(self._device_samplable(s) for s in gen) and self._same_params(gen)
+                    # every sequence carries its own sampler record on the device: mixed parameters share one step
+                    device_sampling = all(self._device_samplable(s) for s in gen)
                     if device_sampling:
-                        p = gen[0].req.sampling
-                        self.eng.sampling = dict(top_k=p.top_k, top_p=p.top_p, min_p=p.min_p, temp=p.temperature, seed=p.seed)
                         out = self.eng.decode(sids, toks, sample=True)
                         new = out.cpu().tolist()
                         for s in gen:
@@ -354,13 +356,6 @@ class Scheduler:
     def _device_samplable(self, s: Slot) -> bool:
         p = s.req.sampling
         return not p.host_only and self.eng.device.type == "cuda"
-
-    @staticmethod
-    def _same_params(slots: list[Slot]) -> bool:
-        p0 = slots[0].req.sampling
-        key = (p0.temperature, p0.top_k, p0.top_p, p0.min_p, p0.seed)
-        return all((s.req.sampling.temperature, s.req.sampling.top_k, s.req.sampling.top_p, s.req.sampling.min_p,
-                    s.req.sampling.seed) == key for s in slots)
 
     def _sample_rows(self, logits: torch.Tensor, slots: list[Slot]) -> list[int]:
         rows = logits.float().cpu()

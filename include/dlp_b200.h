@@ -163,6 +163,21 @@ int dlp_argmax(const float* logits, int R, int V, int ld, int32_t* out, void* st
 int dlp_sample(const float* logits, int R, int V, int ld, int top_k, float top_p, float min_p, float temp,
                uint32_t seed, const int32_t* step_ctr, int32_t* out, void* stream);
 
+/* Same chain with the parameters in device memory: params[slot] (32-byte records), slot = row_slot[row] (row_slot NULL:
+ * slot = row).  temp <= 0 in a record makes that row greedy.  The kernel advances the record's own draw counter, so the
+ * random stream belongs to the request (the host zeroes `ctr` when it writes the record) and nothing request-specific is
+ * baked into the launch: one captured CUDA graph serves every request and rows with different parameters share a batch.
+ * ref: one `common_sampler` + RNG per server slot (llama.cpp/common/sampling.cpp:179-311, tools/server/server-context.cpp:2742). */
+typedef struct dlp_sample_params {
+    int32_t top_k;
+    float top_p, min_p, temp;
+    uint32_t seed;
+    uint32_t ctr;
+    uint32_t reserved[2];
+} dlp_sample_params;
+int dlp_sample_dev(const float* logits, int R, int V, int ld, dlp_sample_params* params, const int32_t* row_slot, int32_t* out,
+                   void* stream);
+
 int dlp_f32_to_f16(const float* in, void* out, size_t n, void* stream);
 
 /* ---- mixture of experts, decode path (graph-capturable: expert ids and weights never leave the device) ----

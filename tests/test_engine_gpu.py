@@ -44,6 +44,58 @@ def test_graph_decode_feeds_back_device_tokens(tmp_models):
     assert a == out
 
 
+def _eager_greedy(path, prompt, n):
+    eng = LlamaEngine(load_weights(path, "cuda"), n_ctx=256, max_seqs=2, page_size=16, max_batch_tokens=64)
+    sid = eng.alloc_seq()
+    out = [int(eng.prefill(sid, prompt).argmax())]
+    for _ in range(n - 1):
+        out.append(int(eng.decode([sid], [out[-1]], sample=False, use_graph=False)[0].argmax()))
+    return out
+
+
+@pytest.mark.parametrize("extra", [[426] * 6, [929] * 5 + [3], [17, 250, 9, 9, 33]])
+def test_graph_capture_keeps_the_pending_token(tmp_models, extra):
+    """The graph warm-up samples into next_tok; the pending input token has to survive it.  The prompts are chosen so that the
+    first generated tokens differ from each other (a dropped token then shows up as a shifted sequence)."""
+    path = tmp_models[("tiny", "F16")]
+    prompt = PROMPT + extra
+    want = _eager_greedy(path, prompt, 12)
+    assert len(set(want[:4])) > 1 or len(set(want)) > 1
+    eng = LlamaEngine(load_weights(path, "cuda"), n_ctx=256, max_seqs=2, page_size=16, max_batch_tokens=64)
+    assert eng.generate(prompt, 12) == want          # device-fed, graph captured on the first decode
+    assert eng.generate(prompt, 12) == want          # replay of the cached graph
+
+
+def test_device_sampler_is_per_request(tmp_models):
+    """Sampling parameters live in per-sequence device records: no graph per seed, and a request's random stream does not depend
+    on what the engine did before (same seed + prompt -> same tokens)."""
+    path = tmp_models[("tiny", "F16")]
+    eng = LlamaEngine(load_weights(path, "cuda"), n_ctx=256, max_seqs=2, page_size=16, max_batch_tokens=64)
+    eng.sampling.update(temp=1.5, top_k=50, top_p=1.0, min_p=0.0, seed=11)
+    a = eng.generate(PROMPT, 16)
+    n_graphs = len(eng._graphs)
+    eng.sampling.update(seed=12)
+    b = eng.generate(PROMPT, 16)
+    eng.sampling.update(seed=11)
+    c = eng.generate(PROMPT, 16)
+    assert a == c and a != b
+    assert len(eng._graphs) == n_graphs              # new seeds did not capture new graphs
+    # two sequences with different parameters share one batched step: the greedy one matches the greedy oracle
+    greedy = _eager_greedy(path, PROMPT, 8)
+    s0, s1 = eng.alloc_seq(), eng.alloc_seq()
+    eng.set_seq_sampling(s0, temp=0.0)
+    eng.set_seq_sampling(s1, temp=2.0, top_k=0, top_p=1.0, min_p=0.0, seed=5)
+    t0 = int(eng.prefill(s0, PROMPT).argmax())
+    eng.prefill(s1, PROMPT)
+    assert t0 == greedy[0]
+    toks = torch.tensor([t0, t0], dtype=torch.int32)
+    got = [t0]
+    for _ in range(7):
+        toks = eng.decode([s0, s1], toks if len(got) == 1 else None, sample=True).clone()
+        got.append(int(toks[0]))
+    assert got == greedy
+
+
 def test_batched_decode_matches_single(tmp_models):
     path = tmp_models[("tiny128", "F16")]
     ref = ReferenceModel.from_gguf(path)
