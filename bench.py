@@ -107,6 +107,12 @@ def run_ours(args) -> dict:
 
     path = ensure_model(args.model, args.ftype, rank, barrier)
     comm = None
+    emu = args.emulate_tp if world == 1 else 0
+    if emu > 1:
+        # per-rank view of an emu-way tensor-parallel step on ONE GPU: rank 0's shard, kernels and launch count exactly as under
+        # real TP, its stores landing in its own buffers (no NVLink hop, nobody to wait for).  A profiling aid, not a headline.
+        from distributed_llm_pipeline_b200.parallel.fused import FusedComm
+        comm = FusedComm.make_emulated(emu)
     if grid.tp > 1:
         fused_ok = False
         if args.tp_impl == "fused":
@@ -122,7 +128,7 @@ def run_ours(args) -> dict:
     if grid.pp > 1:
         raise SystemExit("bench.py times the TP family (config 3); the PP path is exercised by tools/dlp_bench.py")
     t_load = time.time()
-    weights = load_weights(path, dev, tp_rank=grid.tp_rank, tp_size=grid.tp)
+    weights = load_weights(path, dev, tp_rank=grid.tp_rank, tp_size=emu if emu > 1 else grid.tp)
     eng = LlamaEngine(weights, n_ctx=args.n_ctx, max_seqs=1, page_size=64, max_batch_tokens=max(args.prefill, 16), comm=comm)
     torch.cuda.synchronize()
     load_s = time.time() - t_load
@@ -249,7 +255,8 @@ def run_ours(args) -> dict:
         "vs_baseline": (value / BASELINE_PUBLISHED) if BASELINE_PUBLISHED else None, "dtype": "fp16" if args.ftype == "F16" else args.ftype,
         "data": "synthetic (random-init GGUF weights, random token ids)",
         "config": {"model": f"{args.model} {args.ftype} GGUF", "global_batch": 1, "seq_len": args.steps + args.warmup + 1,
-                   "parallelism": f"tp{grid.tp}" + (f"-{args.tp_impl}" if grid.tp > 1 else ""), "instrument": "tg (single-stream decode)",
+                   "parallelism": (f"tp{emu}-emulated-rank0 (1 GPU, no NVLink hop; NOT a headline number)" if emu > 1 else
+                                   f"tp{grid.tp}" + (f"-{args.tp_impl}" if grid.tp > 1 else "")), "instrument": "tg (single-stream decode)",
                    "l2": "inputs larger than L2 (weights >> 126 MB stream from HBM every step)"},
         "clocks": clk,
         "e2e": {"value": round(e2e_tok_s, 2), "unit": "tok/s", "h2d_bytes_per_step": 4, "d2h_bytes_per_step": 4},
@@ -257,7 +264,7 @@ def run_ours(args) -> dict:
         "prefill_tok_s": round(prefill_tok_s, 1), "prefill_tokens": args.prefill, "ttft_ms_p50": round(t_pre.item(), 3),
         "weights_gb": round(weights.nbytes() / 1e9, 3), "load_s": round(load_s, 1),
         "blocks_ms": [round(x, 3) for x in blocks_ms], "timed": f"median of {n_blocks} device-timed blocks of {args.steps} steps",
-        "tp_check": tp_check,
+        "tp_check": tp_check, "symm": getattr(comm, "symm_backend", None), "nvls_multicast": bool(getattr(comm, "mc_base", 0)),
         "hbm_frac_of_measured": None,
     }
     try:
@@ -346,6 +353,7 @@ def main():
     ap.add_argument("--n-ctx", type=int, default=2048)
     ap.add_argument("--pp", type=int, default=1)
     ap.add_argument("--blocks", type=int, default=5, help="timed K-step blocks; the median block is reported")
+    ap.add_argument("--emulate-tp", type=int, default=0, help="1 GPU only: time rank 0 of an N-way tensor-parallel step (profiling aid)")
     ap.add_argument("--no-tp-check", action="store_true", help="skip the fused-vs-NCCL greedy token comparison")
     ap.add_argument("--tp-impl", default=os.environ.get("DLP_TP_IMPL", "fused"), choices=["fused", "nccl"])
     args = ap.parse_args()

@@ -247,8 +247,10 @@ __global__ void __launch_bounds__(128) attn_decode_rope_kernel(const AttnParams 
     __shared__ float cl_ml[MAXS][G][2];
 
     trace_event(p.trace, TR_ATTN | TR_BEGIN);
-    pdl_wait();
-    trace_event(p.trace, TR_ATTN | TR_WAITED);
+    // Everything the previous kernel (the QKV mat-vec) did NOT write is fetched before the dependency wait: sequence length,
+    // block table and the step's rotation table come from the bookkeeping kernel at the start of the step (at least two launches
+    // back, hence complete once this grid may start), the cached K/V rows from earlier steps.  Only `qkv` needs the wait, so the
+    // dependent chain length -> page id -> K/V row runs under the predecessor's tail instead of after it.
     const int len = p.kv_len[qi];                      // keys visible to this query, the new token included
     const int n_old = len - 1;                         // ... of which this many are already in the cache
     const int eff = min((int)gridDim.x, max(1, (len + 63) / 64));
@@ -260,22 +262,23 @@ __global__ void __launch_bounds__(128) attn_decode_rope_kernel(const AttnParams 
     const bool owns_new = active && end == len;
     const int* bt = p.block_table + (size_t)(p.bt_row ? p.bt_row[qi] : qi) * p.max_pages;
     const float* row = qkv + (size_t)qi * H * D;
+    uint4 kr[NV], vr[NV], kn[NV], vn[NV];
+    auto fetch = [&](int tok0, uint4 (&kd)[NV], uint4 (&vd)[NV]) {
+        const int tok = min(tok0 + grp, end_c - 1);
+        const int page = bt[tok / p.page_size], off = tok % p.page_size;
+        const size_t base = (((size_t)page * p.Hkv + kvh) * p.page_size + off) * D + sub * DL;
+#pragma unroll
+        for (int i = 0; i < NV; ++i) {
+            kd[i] = ldg_nc_v4(p.kc + base + i * 8);
+            vd[i] = ldg_nc_v4(p.vc + base + i * 8);
+        }
+    };
+    const int t_first = begin + warp * 4;
+    if (active && t_first < end_c) fetch(t_first, kr, vr);
+    pdl_wait();
+    trace_event(p.trace, TR_ATTN | TR_WAITED);
 
     if (active) {
-        // the first K/V rows are requested before the Q / rotation work so that both latencies overlap
-        uint4 kr[NV], vr[NV], kn[NV], vn[NV];
-        auto fetch = [&](int tok0, uint4 (&kd)[NV], uint4 (&vd)[NV]) {
-            const int tok = min(tok0 + grp, end_c - 1);
-            const int page = bt[tok / p.page_size], off = tok % p.page_size;
-            const size_t base = (((size_t)page * p.Hkv + kvh) * p.page_size + off) * D + sub * DL;
-#pragma unroll
-            for (int i = 0; i < NV; ++i) {
-                kd[i] = ldg_nc_v4(p.kc + base + i * 8);
-                vd[i] = ldg_nc_v4(p.vc + base + i * 8);
-            }
-        };
-        const int t_first = begin + warp * 4;
-        if (t_first < end_c) fetch(t_first, kr, vr);
 
         // rotation terms of the DL dims this lane owns (shared by the G query heads and the new key): the per-step table
         // [nq][D/2] of (cos, sin) written by advance_rope_kernel once for all layers, or computed here

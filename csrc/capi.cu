@@ -91,21 +91,21 @@ int dlp_gemv(const dlp_weight* w0, const dlp_weight* w1, const void* x, const fl
 
 static void fill_ar(GemvParams& p, const dlp_ar_in* in, const dlp_ar_out* out) {
     if (in && in->buf) {
-        p.ar_in.buf = in->buf; p.ar_in.flags = in->flags; p.ar_in.epoch = in->epoch; p.ar_in.h_out = in->h_out;
+        p.ar_in.buf = in->buf; p.ar_in.epoch = in->epoch; p.ar_in.h_out = in->h_out;
         p.ar_in.error = in->error; p.ar_in.tp = in->tp;
     }
     if (out) {
-        for (int i = 0; i < 8; ++i) { p.ar_out.peer_buf[i] = out->peer_buf[i]; p.ar_out.peer_flags[i] = out->peer_flags[i]; }
-        p.ar_out.epoch = out->epoch; p.ar_out.done_counter = out->done_counter; p.ar_out.rank = out->rank; p.ar_out.tp = out->tp;
+        for (int i = 0; i < 8; ++i) p.ar_out.peer_buf[i] = out->peer_buf[i];
+        p.ar_out.mc_buf = out->mc_buf; p.ar_out.epoch = out->epoch; p.ar_out.rank = out->rank; p.ar_out.tp = out->tp;
     }
 }
 
 int dlp_gemv_tp(const dlp_weight* w0, const dlp_weight* w1, const void* x, const float* norm_w, float eps, void* y,
                 int ldy, int out_mode, int T, const dlp_ar_in* ar_in, const dlp_ar_out* ar_out, void* stream) {
     DLP_REQUIRE(w0 && w0->base && x, "dlp_gemv_tp: null argument");
-    DLP_REQUIRE(out_mode != DLP_OUT_PUSH_F32 || (ar_out && ar_out->epoch && ar_out->done_counter), "dlp_gemv_tp: push needs ar_out");
+    DLP_REQUIRE(out_mode != DLP_OUT_PUSH_F32 || (ar_out && ar_out->epoch && T <= AR_MAX_T), "dlp_gemv_tp: push needs ar_out");
     DLP_REQUIRE(out_mode == DLP_OUT_PUSH_F32 || y, "dlp_gemv_tp: null output");
-    DLP_REQUIRE(!(ar_in && ar_in->buf) || (ar_in->flags && ar_in->epoch && ar_in->h_out && norm_w), "dlp_gemv_tp: incomplete ar_in");
+    DLP_REQUIRE(!(ar_in && ar_in->buf) || (ar_in->epoch && ar_in->h_out && norm_w), "dlp_gemv_tp: incomplete ar_in");
     GemvParams p;
     memset(&p, 0, sizeof(p));
     p.w0 = to_qw(w0);
@@ -137,8 +137,18 @@ int dlp_moe_route(const float* logits, int T, int n_expert, int top_k, int32_t* 
 int dlp_ar_consume(const float* h_in, float* h_out, const dlp_ar_in* ar_in, int E, int T, void* stream) {
     DLP_REQUIRE(h_in && h_out && ar_in && ar_in->buf, "dlp_ar_consume: null argument");
     ArIn a;
-    a.buf = ar_in->buf; a.flags = ar_in->flags; a.epoch = ar_in->epoch; a.h_out = h_out; a.error = ar_in->error; a.tp = ar_in->tp;
+    a.buf = ar_in->buf; a.epoch = ar_in->epoch; a.h_out = h_out; a.error = ar_in->error; a.tp = ar_in->tp;
     return ar_consume(h_in, h_out, a, E, T, (cudaStream_t)stream);
+}
+
+int dlp_argmax_tp(const float* logits, int R, int V, int ld, int v0, const dlp_tokx* x, int32_t* out, void* stream) {
+    DLP_REQUIRE(logits && x && out, "dlp_argmax_tp: null argument");
+    TokX t;
+    for (int i = 0; i < 8; ++i) t.peer_slots[i] = reinterpret_cast<unsigned long long*>(x->peer_slots[i]);
+    t.mc_slots = reinterpret_cast<unsigned long long*>(x->mc_slots);
+    t.slots = reinterpret_cast<unsigned long long*>(x->slots);
+    t.epoch = x->epoch; t.error = x->error; t.rank = x->rank; t.tp = x->tp;
+    return argmax_tp(logits, R, V, ld, v0, t, out, (cudaStream_t)stream);
 }
 
 int dlp_gemm_sp(const dlp_weight* w0, const dlp_weight* w1, const void* x, int ldx, void* y, int ldy, int epilogue, int T,

@@ -9,6 +9,7 @@
 #include <string.h>
 
 #include "kernels.cuh"
+#include "tpcomm.cuh"
 
 namespace dlp {
 
@@ -17,29 +18,108 @@ __global__ void bump_kernel(int* ctr) { pdl_wait(); pdl_launch_dependents(); *ct
 __global__ void __launch_bounds__(256) ar_consume_kernel(const float* __restrict__ h_in, float* __restrict__ h_out, const ArIn a, int K, int T) {
     pdl_wait();
     pdl_launch_dependents();
-    if ((int)threadIdx.x < a.tp && !(a.error && *reinterpret_cast<volatile int*>(a.error))) {
-        const uint32_t want = (uint32_t)*a.epoch;
-        const long long t0 = clock64();
-        uint32_t v;
-        do {
-            asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(a.flags + threadIdx.x) : "memory");
-            if (clock64() - t0 > (1ll << 34)) { if (a.error) atomicExch(a.error, 1); break; }
-        } while ((int32_t)(v - want) < 0);
-    }
-    __syncthreads();
-    const int t = blockIdx.x;
-    for (int k = threadIdx.x * 4; k < K; k += blockDim.x * 4) {
-        float4 v = *reinterpret_cast<const float4*>(h_in + (size_t)t * K + k);
-        for (int r = 0; r < a.tp; ++r) {
-            const float4 d = __ldcg(reinterpret_cast<const float4*>(a.buf + ((size_t)r * T + t) * K + k));
-            v.x += d.x; v.y += d.y; v.z += d.z; v.w += d.w;
+    const float* arb = a.buf + ar_parity_off(a.epoch, a.tp, K);
+    for (int t = blockIdx.x; t < T; t += gridDim.x) {
+        for (int k = threadIdx.x * 4; k < K; k += blockDim.x * 4) {
+            float4 v = *reinterpret_cast<const float4*>(h_in + (size_t)t * K + k);
+            for (int r = 0; r < a.tp; ++r) {
+                const float4 d = ar_take4(arb + ((size_t)r * AR_MAX_T + t) * K + k, a.error);
+                v.x += d.x; v.y += d.y; v.z += d.z; v.w += d.w;
+            }
+            *reinterpret_cast<float4*>(h_out + (size_t)t * K + k) = v;
         }
-        *reinterpret_cast<float4*>(h_out + (size_t)t * K + k) = v;
     }
+    ar_rearm(a.buf, a.epoch, a.tp, K);
+}
+
+__global__ void fill_u32_kernel(uint32_t* p, size_t n, uint32_t v) {
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) p[i] = v;
+}
+int fill_u32(uint32_t* p, size_t n, uint32_t v, cudaStream_t s) {
+    fill_u32_kernel<<<(unsigned)((n + 1023) / 1024 < 1184 ? (n + 1023) / 1024 : 1184), 256, 0, s>>>(p, n, v);
+    DLP_LAUNCH_CHECK();
+    return 0;
+}
+
+// Sharded greedy sampling under tensor parallelism: every rank holds the logits of its vocabulary shard only.  One CTA per
+// batch row finds the shard's best (value, index), stores it as one 8-byte word into slot [rank][row] of every rank (a value is
+// its own arrival signal: 0 = empty), waits for the tp words and keeps the global winner - the same on every rank (ties go to
+// the lower token id).  No logits all-gather, no NCCL call inside the decode step.
+// ref: the reference gathers full logits on the hub GPU and samples on the CPU (llama-context.cpp:1591, server-context.cpp:2742).
+__device__ __forceinline__ uint32_t ord_f32(float f) {
+    const uint32_t u = __float_as_uint(f);
+    return (u & 0x80000000u) ? ~u : (u | 0x80000000u);
+}
+__global__ void __launch_bounds__(1024) argmax_tp_kernel(const float* __restrict__ logits, int V, int ld, int v0, const TokX x, int* __restrict__ out) {
+    __shared__ float sv[32];
+    __shared__ int si[32];
+    pdl_wait();
+    pdl_launch_dependents();
+    const int b = blockIdx.x;
+    const float* row = logits + (size_t)b * ld;
+    float best = -INFINITY;
+    int bi = 0;
+    for (int i = threadIdx.x; i < V; i += blockDim.x) {
+        const float v = row[i];
+        if (v > best) { best = v; bi = i; }
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        const float ov = __shfl_xor_sync(0xffffffffu, best, o);
+        const int oi = __shfl_xor_sync(0xffffffffu, bi, o);
+        if (ov > best || (ov == best && oi < bi)) { best = ov; bi = oi; }
+    }
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    if (lane == 0) { sv[warp] = best; si[warp] = bi; }
+    __syncthreads();
+    if (warp != 0) return;
+    const int nw = blockDim.x >> 5;
+    best = lane < nw ? sv[lane] : -INFINITY;
+    bi = lane < nw ? si[lane] : 0x7fffffff;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        const float ov = __shfl_xor_sync(0xffffffffu, best, o);
+        const int oi = __shfl_xor_sync(0xffffffffu, bi, o);
+        if (ov > best || (ov == best && oi < bi)) { best = ov; bi = oi; }
+    }
+    const int par = *x.epoch & 1;
+    const size_t slot = ((size_t)par * x.tp + x.rank) * AR_MAX_T + b;
+    if (lane == 0) {   // larger word = better candidate: value first, then the lower global token id
+        const unsigned long long w = ((unsigned long long)ord_f32(best) << 32) | (0xFFFFFFFFu - (uint32_t)(v0 + bi));
+        if (x.mc_slots != nullptr) {
+            asm volatile("multimem.st.relaxed.sys.global.u64 [%0], %1;" ::"l"(x.mc_slots + slot), "l"(w) : "memory");
+        } else {
+            for (int pr = 0; pr < x.tp; ++pr) asm volatile("st.relaxed.sys.global.u64 [%0], %1;" ::"l"(x.peer_slots[pr] + slot), "l"(w) : "memory");
+        }
+    }
+    unsigned long long w = 0;
+    if (lane < x.tp) {
+        const unsigned long long* p = x.slots + ((size_t)par * x.tp + lane) * AR_MAX_T + b;
+        const long long t0 = clock64();
+        while (true) {
+            asm volatile("ld.volatile.global.u64 %0, [%1];" : "=l"(w) : "l"(p) : "memory");
+            if (w != 0) break;
+            if (x.error && *reinterpret_cast<volatile int*>(x.error)) break;
+            if (clock64() - t0 > (1ll << 34)) { if (x.error) atomicExch(x.error, 1); break; }
+        }
+        x.slots[((size_t)(par ^ 1) * x.tp + lane) * AR_MAX_T + b] = 0;   // re-arm the other parity
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        const unsigned long long ow = __shfl_xor_sync(0xffffffffu, w, o);
+        w = ow > w ? ow : w;
+    }
+    if (lane == 0) out[b] = (int)(0xFFFFFFFFu - (uint32_t)(w & 0xFFFFFFFFull));
+}
+
+int argmax_tp(const float* logits, int R, int V, int ld, int v0, const TokX& x, int* out, cudaStream_t s) {
+    DLP_REQUIRE(R >= 1 && R <= AR_MAX_T && V > 0 && x.tp >= 1 && x.tp <= 8 && x.slots && x.epoch, "argmax_tp: bad argument");
+    DLP_CHECK_CUDA(launch_pdl(argmax_tp_kernel, dim3(R), dim3(1024), 0, s, logits, V, ld, v0, x, out));
+    return 0;
 }
 
 int ar_consume(const float* h_in, float* h_out, const ArIn& a, int K, int T, cudaStream_t s) {
-    DLP_REQUIRE(a.buf && a.flags && a.epoch && a.tp >= 1 && a.tp <= 8, "ar_consume: bad descriptor");
+    DLP_REQUIRE(a.buf && a.epoch && a.tp >= 1 && a.tp <= 8 && T >= 1 && T <= AR_MAX_T && K % 4 == 0, "ar_consume: bad descriptor");
     DLP_CHECK_CUDA(launch_pdl(ar_consume_kernel, dim3(T), dim3(256), 0, s, h_in, h_out, a, K, T));
     return 0;
 }
@@ -158,6 +238,10 @@ int dlp_ipc_close(void* ptr) {
 int dlp_bump(int32_t* ctr, void* stream) {
     DLP_REQUIRE(ctr, "dlp_bump: null argument");
     return bump(ctr, (cudaStream_t)stream);
+}
+int dlp_fill_u32(void* p, size_t n_words, uint32_t value, void* stream) {
+    DLP_REQUIRE(p && n_words > 0, "dlp_fill_u32: bad argument");
+    return fill_u32(reinterpret_cast<uint32_t*>(p), n_words, value, (cudaStream_t)stream);
 }
 int dlp_memcpy_d2h(void* dst, const void* src, size_t bytes) {
     DLP_CHECK_CUDA(cudaMemcpy(dst, src, bytes, cudaMemcpyDeviceToHost));

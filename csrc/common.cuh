@@ -49,7 +49,7 @@ int sm_count();  // cached multiprocessor count of the current device
 // instrumented kernel appends (event id << 48 | globaltimer ns) records.  buf[0] = count, buf[1] = capacity, records follow.
 unsigned long long* trace_buffer();
 void set_trace_buffer(unsigned long long* buf);
-enum TraceId : unsigned { TR_BEGIN = 0, TR_WAITED = 1, TR_MAIN_DONE = 2, TR_END = 3, TR_GEMV = 1 << 8, TR_ROPE = 2 << 8, TR_ATTN = 3 << 8 };
+enum TraceId : unsigned { TR_BEGIN = 0, TR_WAITED = 1, TR_MAIN_DONE = 2, TR_END = 3, TR_AR_DONE = 4, TR_GEMV = 1 << 8, TR_ROPE = 2 << 8, TR_ATTN = 3 << 8 };
 // One-time per-(device, kernel) configuration (cudaFuncSetAttribute is a per-device setting): true exactly once per pair.
 bool first_use_on_device(const void* kernel);
 bool pdl_enabled();  // programmatic dependent launch between consecutive kernels (env DLP_PDL=0 disables)
@@ -282,6 +282,26 @@ inline cudaError_t launch_pdl(void (*kern)(KArgs...), dim3 grid, dim3 block, siz
     attr[0].val.programmaticStreamSerializationAllowed = pdl_enabled() ? 1 : 0;
     cfg.attrs = attr;
     cfg.numAttrs = 1;
+    return cudaLaunchKernelEx(&cfg, kern, static_cast<KArgs>(args)...);
+}
+// same, as thread-block clusters of `cluster` CTAs along x (grid.x must be a multiple of it; 1 = plain launch)
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_pdl_cluster(void (*kern)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t stream, unsigned cluster,
+                                      Args&&... args) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = grid;
+    cfg.blockDim = block;
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = stream;
+    cudaLaunchAttribute attr[2];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = pdl_enabled() ? 1 : 0;
+    attr[1].id = cudaLaunchAttributeClusterDimension;
+    attr[1].val.clusterDim.x = cluster;
+    attr[1].val.clusterDim.y = 1;
+    attr[1].val.clusterDim.z = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = cluster > 1 ? 2 : 1;
     return cudaLaunchKernelEx(&cfg, kern, static_cast<KArgs>(args)...);
 }
 #endif

@@ -6,40 +6,22 @@
 // Differences by design: activations stay fp16/fp32 (no q8_1 activation quantise pass), RMSNorm is fused
 // into the prologue (each CTA normalises x once into shared memory), the residual add is fused into the
 // epilogue, and every lane keeps 8 x 16-byte weight loads in flight (two row streams x 4-deep unroll).
+#include <cooperative_groups.h>
 #include <stdlib.h>
 
 #include "kernels.cuh"
+#include "tpcomm.cuh"
 
 namespace dlp {
 
 __device__ __forceinline__ float gv_silu(float x) { return x / (1.f + __expf(-x)); }
 
 // ---- fused all-reduce, consumer side -------------------------------------------------------------
-// Row-parallel partial results of the previous GEMV arrive in this rank's `ar_in.buf` ([tp][T][K] fp32), pushed
-// by every peer (and by ourselves) over NVLink together with a per-peer epoch flag.  The consumer waits for
-// the tp flags, then forms  h_out = h_in + sum_p buf[p]  in rank order (bitwise identical on every rank).
-__device__ __forceinline__ uint32_t ld_acquire_sys_u32(const uint32_t* p) {
-    uint32_t v;
-    asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
-    return v;
-}
-__device__ __forceinline__ void st_release_sys_u32(uint32_t* p, uint32_t v) {
-    asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
-}
-
-__device__ __forceinline__ void ar_wait(const ArIn& a) {
-    if ((int)threadIdx.x < a.tp && !(a.error && *reinterpret_cast<volatile int*>(a.error))) {
-        const uint32_t want = (uint32_t)*a.epoch;
-        const long long t0 = clock64();
-        while ((int32_t)(ld_acquire_sys_u32(a.flags + threadIdx.x) - want) < 0) {
-            if (clock64() - t0 > (1ll << 34)) {  // ~9 s: a peer died or diverged; record once, later waits are skipped
-                if (a.error) atomicExch(a.error, 1);
-                break;
-            }
-        }
-    }
-    __syncthreads();
-}
+// Row-parallel partial results of the previous mat-vec arrive in this rank's buffer of the site ([parity][tp][AR_MAX_T][K] fp32),
+// stored by every rank (ourselves included) over NVLink.  The consumer spins on the values themselves (tpcomm.cuh), forms
+// h_out = h_in + sum_p buf[p]  in rank order (bitwise identical on every rank) and re-arms the other parity.
+// fp32 staging of the folded residual row(s) behind the fp16 activations: one row, or two (ping-pong) when NT > 1
+__host__ __device__ __forceinline__ size_t ar_stage_bytes(bool ar, int NT, int K) { return ar ? (size_t)(NT > 1 ? 2 : 1) * K * 4 : 0; }
 
 template <int NT>
 __device__ __forceinline__ void stage_x(const GemvParams& p, int K, __half* xs, float* red) {
@@ -54,29 +36,16 @@ __device__ __forceinline__ void stage_x(const GemvParams& p, int K, __half* xs, 
         return;
     }
     const float* h = reinterpret_cast<const float*>(p.x);
-    const bool ar = p.ar_in.buf != nullptr;
-    if (ar) ar_wait(p.ar_in);
-    float* hs = reinterpret_cast<float*>(xs + (size_t)NT * K);  // fp32 staging of the reduced row (AR only)
-#pragma unroll
-    for (int t = 0; t < NT; ++t) {
+    auto normalise = [&](const float* src, int t) {   // src: fp32 row (global h or the staged, folded row)
         float ss = 0.f;
         for (int k = tid * 4; k < K; k += nth * 4) {
-            float4 v = *reinterpret_cast<const float4*>(h + (size_t)t * K + k);
-            if (ar) {
-                for (int r = 0; r < p.ar_in.tp; ++r) {
-                    const float4 d = __ldcg(reinterpret_cast<const float4*>(p.ar_in.buf + ((size_t)r * NT + t) * K + k));
-                    v.x += d.x; v.y += d.y; v.z += d.z; v.w += d.w;
-                }
-                *reinterpret_cast<float4*>(hs + k) = v;
-                if (blockIdx.x == 0) *reinterpret_cast<float4*>(p.ar_in.h_out + (size_t)t * K + k) = v;
-            }
+            const float4 v = *reinterpret_cast<const float4*>(src + k);
             ss += v.x * v.x + v.y * v.y + v.z * v.z + v.w * v.w;
         }
         ss = block_sum(ss, red);
         const float rs = rsqrtf(ss / (float)K + p.eps);
         for (int k = tid * 4; k < K; k += nth * 4) {
-            const float4 v = ar ? *reinterpret_cast<const float4*>(hs + k)
-                                : *reinterpret_cast<const float4*>(h + (size_t)t * K + k);
+            const float4 v = *reinterpret_cast<const float4*>(src + k);
             const float4 g = *reinterpret_cast<const float4*>(p.norm_w + k);
             __half2 a = __floats2half2_rn(v.x * rs * g.x, v.y * rs * g.y);
             __half2 b = __floats2half2_rn(v.z * rs * g.z, v.w * rs * g.w);
@@ -85,26 +54,53 @@ __device__ __forceinline__ void stage_x(const GemvParams& p, int K, __half* xs, 
             o.y = *reinterpret_cast<uint32_t*>(&b);
             *reinterpret_cast<uint2*>(xs + (size_t)t * K + k) = o;
         }
-        __syncthreads();  // hs is reused by the next token
+    };
+    if (p.ar_in.buf == nullptr) {
+#pragma unroll
+        for (int t = 0; t < NT; ++t) normalise(h + (size_t)t * K, t);
+        __syncthreads();
+        return;
     }
-    __syncthreads();
-}
-
-// ---- fused all-reduce, producer side ----------------------------------------------------------------
-// After a CTA has pushed all its rows, thread 0 fences at system scope and bumps a local counter; the CTA that
-// observes the final count publishes this rank's epoch flag to every peer (release at system scope).
-__device__ __forceinline__ void ar_signal(const ArOut& a) {
-    __syncthreads();
-    if (threadIdx.x == 0) {
-        __threadfence_system();
-        const unsigned prev = atomicAdd(a.done_counter, 1u);
-        if (prev == gridDim.x - 1) {
-            *a.done_counter = 0;  // ready for the next launch that uses this counter
-            __threadfence_system();
-            const uint32_t e = (uint32_t)*a.epoch;
-            for (int pr = 0; pr < a.tp; ++pr) st_release_sys_u32(a.peer_flags[pr] + a.rank, e);
+    // Fold the all-reduce.  Every CTA needs the whole folded row, but reading tp x K partials in each of ~300 CTAs costs more
+    // than the mat-vec itself at tp = 8 (measured: 11 us per site).  The CTAs of a thread-block cluster therefore split the row:
+    // each folds K / C columns (all tp loads of a thread are issued before the first is checked) and stores its slice into the
+    // shared memory of all C cluster members through DSMEM; one cluster barrier later everybody holds the full row.
+    namespace cg = cooperative_groups;
+    cg::cluster_group cl = cg::this_cluster();
+    const unsigned C = cl.num_blocks(), cr = cl.block_rank();
+    const int tp = p.ar_in.tp;
+    const float* arb = p.ar_in.buf + ar_parity_off(p.ar_in.epoch, tp, K);
+    float* hs = reinterpret_cast<float*>(xs + (size_t)NT * K);
+    const int kslice = K / (int)C, k_lo = (int)cr * kslice;
+    float* peer_hs[8];
+#pragma unroll
+    for (unsigned c = 0; c < 8; ++c) peer_hs[c] = c < C ? cl.map_shared_rank(hs, c) : nullptr;
+#pragma unroll
+    for (int t = 0; t < NT; ++t) {
+        const int boff = NT > 1 ? (t & 1) * K : 0;
+        for (int k = k_lo + tid * 4; k < k_lo + kslice; k += nth * 4) {
+            float4 v = *reinterpret_cast<const float4*>(h + (size_t)t * K + k);
+            float4 d[8];
+#pragma unroll
+            for (int r = 0; r < 8; ++r)
+                if (r < tp) d[r] = ld_volatile_f4(arb + ((size_t)r * AR_MAX_T + t) * K + k);
+#pragma unroll
+            for (int r = 0; r < 8; ++r)
+                if (r < tp) {
+                    if (ar_has_empty(d[r])) d[r] = ar_take4(arb + ((size_t)r * AR_MAX_T + t) * K + k, p.ar_in.error);
+                    v.x += d[r].x; v.y += d[r].y; v.z += d[r].z; v.w += d[r].w;
+                }
+            if (blockIdx.x < C) *reinterpret_cast<float4*>(p.ar_in.h_out + (size_t)t * K + k) = v;
+#pragma unroll
+            for (unsigned c = 0; c < 8; ++c)
+                if (c < C) *reinterpret_cast<float4*>(peer_hs[c] + boff + k) = v;
         }
+        cl.sync();     // slices of token t are in everybody's staging row; rows of token t - 2 are no longer read by anyone
+        normalise(hs + boff, t);
     }
+    trace_event(p.trace, TR_GEMV | TR_AR_DONE);
+    ar_rearm(p.ar_in.buf, p.ar_in.epoch, tp, K);   // the other parity: next used two steps from now
+    __syncthreads();
 }
 
 template <int NT>
@@ -119,6 +115,15 @@ __device__ __forceinline__ void gv_write(const GemvParams& p, int row, float (&a
         }
         return;
     }
+    if (p.out_mode == GV_PUSH_F32) {   // partial sums of this rank's K shard -> slot [rank][t][row, row+1] of every rank's buffer
+        if (lane < NT) {
+            float a0 = 0.f, a1 = 0.f;
+#pragma unroll
+            for (int t = 0; t < NT; ++t) if (t == lane) { a0 = acc[0][t]; a1 = acc[1][t]; }
+            ar_push2(p.ar_out, ar_parity_off(p.ar_out.epoch, p.ar_out.tp, p.w0.N), lane, p.w0.N, row, a0, a1);
+        }
+        return;
+    }
     if (lane < 2 * NT) {
         const int s = lane & 1, t = lane >> 1;
         float v = 0.f;
@@ -126,11 +131,7 @@ __device__ __forceinline__ void gv_write(const GemvParams& p, int row, float (&a
         for (int tt = 0; tt < NT; ++tt) if (tt == t) v = s ? acc[1][tt] : acc[0][tt];
         const size_t o = (size_t)t * p.ldy + row + s;
         if (row + s < p.w0.N) {
-            if (p.out_mode == GV_PUSH_F32) {
-                // partial sum of this rank's K shard -> slot [rank][t][row] of every peer's reduce buffer
-                for (int pr = 0; pr < p.ar_out.tp; ++pr)
-                    p.ar_out.peer_buf[pr][((size_t)p.ar_out.rank * NT + t) * p.w0.N + row + s] = v;
-            } else if (p.out_mode == GV_STORE_F16) reinterpret_cast<__half*>(p.y)[o] = __float2half_rn(v);
+            if (p.out_mode == GV_STORE_F16) reinterpret_cast<__half*>(p.y)[o] = __float2half_rn(v);
             else if (p.out_mode == GV_STORE_F32) reinterpret_cast<float*>(p.y)[o] = v;
             else reinterpret_cast<float*>(p.y)[o] += v;  // GV_ADD_F32: each output has exactly one writer
         }
@@ -211,7 +212,6 @@ __global__ void __launch_bounds__(256) gemv_dense_kernel(const GemvParams p) {
         gv_write<NT>(p, row, acc, dual, lane);
     }
     pdl_launch_dependents();
-    if (p.out_mode == GV_PUSH_F32) ar_signal(p.ar_out);
 }
 
 
@@ -236,7 +236,7 @@ __global__ void __launch_bounds__(256, 2) gemv_dense_v3_kernel(const GemvParams 
     const bool dual = p.out_mode == GV_SWIGLU_F16;
     const int rpu = dual ? 1 : 2;              // rows per unit (dual: one gate row + the matching up row)
     __half* xs = reinterpret_cast<__half*>(gv_smem);
-    size_t off = (size_t)NT * K * 2 + (p.ar_in.buf ? (size_t)K * 4 : 0);
+    size_t off = (size_t)NT * K * 2 + ar_stage_bytes(p.ar_in.buf != nullptr, NT, K);
     off = (off + 15) & ~size_t(15);
     float* partial = reinterpret_cast<float*>(gv_smem + off);   // [n_groups][KC][2][NT]
     __shared__ float red[32];
@@ -361,6 +361,20 @@ __global__ void __launch_bounds__(256, 2) gemv_dense_v3_kernel(const GemvParams 
     __syncthreads();
     // fixed-order combination of the K-chunk partials + fused epilogue
     const int n_rows = (g_hi - g_lo) * rpu;
+    if (p.out_mode == GV_PUSH_F32) {   // one thread per (row pair, token): 8-byte self-signalling stores into every rank's buffer
+        const size_t poff = ar_parity_off(p.ar_out.epoch, p.ar_out.tp, N);
+        for (int idx = threadIdx.x; idx < (g_hi - g_lo) * NT; idx += blockDim.x) {
+            const int g = idx / NT, t = idx % NT;
+            float v0 = 0.f, v1 = 0.f;
+            for (int c = 0; c < KC; ++c) {
+                const float* q = partial + ((size_t)g * KC + c) * 2 * NT;
+                v0 += q[t];
+                v1 += q[NT + t];
+            }
+            ar_push2(p.ar_out, poff, t, N, (g_lo + g) * 2, v0 * oscale, v1 * oscale);
+        }
+        return;
+    }
     for (int idx = threadIdx.x; idx < n_rows * NT; idx += blockDim.x) {
         const int rl = idx / NT, t = idx % NT;
         const int g = rl / rpu, m = dual ? 0 : (rl % rpu);
@@ -374,16 +388,45 @@ __global__ void __launch_bounds__(256, 2) gemv_dense_v3_kernel(const GemvParams 
         }
         if (!dual) v0 *= oscale;
         const size_t o = (size_t)t * p.ldy + row;
-        if (p.out_mode == GV_PUSH_F32) {
-            for (int pr = 0; pr < p.ar_out.tp; ++pr) p.ar_out.peer_buf[pr][((size_t)p.ar_out.rank * NT + t) * N + row] = v0;
-        } else if (p.out_mode == GV_STORE_F16) reinterpret_cast<__half*>(p.y)[o] = __float2half_rn(v0);
+        if (p.out_mode == GV_STORE_F16) reinterpret_cast<__half*>(p.y)[o] = __float2half_rn(v0);
         else if (p.out_mode == GV_STORE_F32) reinterpret_cast<float*>(p.y)[o] = v0;
         else if (p.out_mode == GV_ADD_F32) reinterpret_cast<float*>(p.y)[o] += v0;
         else reinterpret_cast<__half*>(p.y)[o] = __float2half_rn(gv_silu(v0) * v1);
     }
-    if (p.out_mode == GV_PUSH_F32) ar_signal(p.ar_out);
     trace_event(p.trace, TR_GEMV | TR_END);
     trace_event_cta(p.trace, TR_END);
+}
+
+// CTAs per cluster for kernels that fold an all-reduce in their prologue (stage_x): the cluster splits the fold.
+// Pairs by default: 148 SMs hold 74 pairs exactly, while clusters of 4 strand 16 SMs (measured: 66 of the 74 clusters of a
+// 296-CTA grid were resident, the rest ran as a second wave and doubled the kernel time).  DLP_AR_CLUSTER=n overrides.
+static unsigned ar_cluster(const GemvParams& p, int blocks) {
+    if (p.ar_in.buf == nullptr) return 1;
+    static int forced = -1;
+    if (forced < 0) { const char* e = getenv("DLP_AR_CLUSTER"); forced = e ? atoi(e) : 0; }
+    unsigned c = forced > 0 ? (unsigned)forced : 2u;
+    while (c > 1 && (p.w0.K % (int)(4 * c) != 0 || blocks < (int)c)) c >>= 1;
+    return c;
+}
+// largest grid (in CTAs) of `cl`-CTA clusters that is resident at once; the balanced row ranges of the kernels take any grid size
+template <typename Kern>
+static int resident_cluster_blocks(Kern kern, unsigned cl, size_t smem, int threads, int want) {
+    if (cl <= 1) return want;
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3((unsigned)want);
+    cfg.blockDim = dim3((unsigned)threads);
+    cfg.dynamicSmemBytes = smem;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = cl;
+    attr[0].val.clusterDim.y = 1;
+    attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    int n = 0;
+    if (cudaOccupancyMaxActiveClusters(&n, kern, &cfg) != cudaSuccess || n <= 0) { cudaGetLastError(); return want; }
+    const int cap = n * (int)cl;
+    return want < cap ? want : cap;
 }
 
 template <typename Kern>
@@ -395,11 +438,18 @@ static int launch_gemv_v3(Kern kern, const GemvParams& p, int U, size_t x_smem, 
     const int groups = (p.w0.N + rpu - 1) / rpu;
     int blocks = sm_count() * 2;
     if (blocks > groups) blocks = groups;
+    blocks -= blocks % (int)ar_cluster(p, blocks);
     const int KC = p.w0.K / (256 * U);
     const int max_groups = (groups + blocks - 1) / blocks + 1;
     const size_t smem = ((x_smem + 15) & ~size_t(15)) + (size_t)max_groups * KC * 2 * p.T * sizeof(float);
     DLP_REQUIRE(smem <= 100 * 1024, "gemv v3: %zu bytes of shared memory needed", smem);
-    DLP_CHECK_CUDA(launch_pdl(kern, dim3(blocks), dim3(256), smem, stream, p));
+    const unsigned cl = ar_cluster(p, blocks);
+    blocks = resident_cluster_blocks(kern, cl, smem, 256, blocks);   // (fewer CTAs only lengthen the row ranges: smem bound still holds
+    blocks -= blocks % (int)cl;                                        //  when the cap is >= 1/2 of the request; checked below)
+    DLP_REQUIRE(((size_t)((groups + blocks - 1) / blocks + 1) * KC * 2 * p.T * sizeof(float)) + ((x_smem + 15) & ~size_t(15)) <= 100 * 1024,
+                "gemv v3: row range too long for shared memory");
+    const size_t smem2 = ((x_smem + 15) & ~size_t(15)) + (size_t)((groups + blocks - 1) / blocks + 1) * KC * 2 * p.T * sizeof(float);
+    DLP_CHECK_CUDA(launch_pdl_cluster(kern, dim3(blocks), dim3(256), smem2, stream, cl, p));
     return 0;
 }
 
@@ -426,7 +476,7 @@ __global__ void __launch_bounds__(288, 1) gemv_bulk_kernel(const GemvParams p, c
     const uint32_t row_bytes = (uint32_t)K * 2;
     const uint32_t stage_bytes = (uint32_t)R * row_bytes * nmat;
     __half* xs = reinterpret_cast<__half*>(gv_smem);
-    size_t off = (size_t)NT * K * 2 + (p.ar_in.buf ? (size_t)K * 4 : 0);
+    size_t off = (size_t)NT * K * 2 + ar_stage_bytes(p.ar_in.buf != nullptr, NT, K);
     off = (off + 127) & ~size_t(127);
     uint8_t* ring = gv_smem + off;
     off += (size_t)S * stage_bytes;
@@ -529,9 +579,8 @@ __global__ void __launch_bounds__(288, 1) gemv_bulk_kernel(const GemvParams p, c
                         v1 += q[NT + t];
                     }
                     const size_t o = (size_t)t * p.ldy + row;
-                    if (p.out_mode == GV_PUSH_F32) {
-                        for (int pr = 0; pr < p.ar_out.tp; ++pr) p.ar_out.peer_buf[pr][((size_t)p.ar_out.rank * NT + t) * N + row] = v0;
-                    } else if (p.out_mode == GV_STORE_F16) reinterpret_cast<__half*>(p.y)[o] = __float2half_rn(v0);
+                    if (p.out_mode == GV_PUSH_F32) ar_push1(p.ar_out, ar_parity_off(p.ar_out.epoch, p.ar_out.tp, N), t, N, row, v0);
+                    else if (p.out_mode == GV_STORE_F16) reinterpret_cast<__half*>(p.y)[o] = __float2half_rn(v0);
                     else if (p.out_mode == GV_STORE_F32) reinterpret_cast<float*>(p.y)[o] = v0;
                     else if (p.out_mode == GV_ADD_F32) reinterpret_cast<float*>(p.y)[o] += v0;
                     else reinterpret_cast<__half*>(p.y)[o] = __float2half_rn(gv_silu(v0) * v1);
@@ -541,7 +590,6 @@ __global__ void __launch_bounds__(288, 1) gemv_bulk_kernel(const GemvParams p, c
             if (lane == 0) mbar_arrive(&empty[s]);
         }
     }
-    if (p.out_mode == GV_PUSH_F32) ar_signal(p.ar_out);
 }
 
 // picks (R, S) for the bulk kernel; returns false when the shape does not fit its constraints
@@ -571,7 +619,9 @@ static int launch_gemv_bulk(Kern kern, const GemvParams& p, const BulkCfg& cfg, 
         DLP_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 216 * 1024));
     int blocks = sm_count();
     if (blocks > cfg.n_groups) blocks = cfg.n_groups;
-    DLP_CHECK_CUDA(launch_pdl(kern, dim3(blocks), dim3(288), smem, stream, p, cfg));
+    const unsigned cl = ar_cluster(p, blocks);
+    blocks -= blocks % (int)cl;
+    DLP_CHECK_CUDA(launch_pdl_cluster(kern, dim3(blocks), dim3(288), smem, stream, cl, p, cfg));
     return 0;
 }
 
@@ -582,7 +632,7 @@ __global__ void __launch_bounds__(256) gemv_quant_kernel(const GemvParams p) {
     const int K = p.w0.K, N = p.w0.N;
     __half* xs = reinterpret_cast<__half*>(gv_smem);
     // [NT][K/16] sums of x per 16 elements (placed after the optional fp32 AR staging row)
-    float* xsum = reinterpret_cast<float*>(gv_smem + (size_t)NT * K * 2 + (p.ar_in.buf ? (size_t)K * 4 : 0));
+    float* xsum = reinterpret_cast<float*>(gv_smem + (size_t)NT * K * 2 + ar_stage_bytes(p.ar_in.buf != nullptr, NT, K));
     __shared__ float red[32];
     pdl_wait();
     stage_x<NT>(p, K, xs, red);
@@ -648,7 +698,6 @@ __global__ void __launch_bounds__(256) gemv_quant_kernel(const GemvParams p) {
         gv_write<NT>(p, row, acc, dual, lane);
     }
     pdl_launch_dependents();
-    if (p.out_mode == GV_PUSH_F32) ar_signal(p.ar_out);
 }
 
 
@@ -809,7 +858,7 @@ __global__ void __launch_bounds__(256, 2) gemv_quant_v3_kernel(const GemvParams 
     const int rpu = dual ? 1 : 2;
     // shared memory: fp16 x [NT][K] (stage_x output, AR staging behind it) | int8 xq [NT][K] | xd [NT][K/32] | xs16 [NT][K/16] | xqs16 [NT][K/16] | partials
     __half* xs = reinterpret_cast<__half*>(gv_smem);
-    size_t off = (size_t)NT * K * 2 + (p.ar_in.buf ? (size_t)K * 4 : 0);
+    size_t off = (size_t)NT * K * 2 + ar_stage_bytes(p.ar_in.buf != nullptr, NT, K);
     off = (off + 15) & ~size_t(15);
     int8_t* xq = reinterpret_cast<int8_t*>(gv_smem + off);
     off += (size_t)NT * K;
@@ -932,6 +981,20 @@ __global__ void __launch_bounds__(256, 2) gemv_quant_v3_kernel(const GemvParams 
     pdl_launch_dependents();
     __syncthreads();
     const int n_rows = (g_hi - g_lo) * rpu;
+    if (p.out_mode == GV_PUSH_F32) {   // one thread per (row pair, token): 8-byte self-signalling stores into every rank's buffer
+        const size_t poff = ar_parity_off(p.ar_out.epoch, p.ar_out.tp, N);
+        for (int idx = threadIdx.x; idx < (g_hi - g_lo) * NT; idx += blockDim.x) {
+            const int g = idx / NT, t = idx % NT;
+            float v0 = 0.f, v1 = 0.f;
+            for (int c = 0; c < KC; ++c) {
+                const float* q = partial + ((size_t)g * KC + c) * 2 * NT;
+                v0 += q[t];
+                v1 += q[NT + t];
+            }
+            ar_push2(p.ar_out, poff, t, N, (g_lo + g) * 2, v0 * oscale, v1 * oscale);
+        }
+        return;
+    }
     for (int idx = threadIdx.x; idx < n_rows * NT; idx += blockDim.x) {
         const int rl = idx / NT, t = idx % NT;
         const int g = rl / rpu, m = dual ? 0 : (rl % rpu);
@@ -945,14 +1008,11 @@ __global__ void __launch_bounds__(256, 2) gemv_quant_v3_kernel(const GemvParams 
         }
         if (!dual) v0 *= oscale;
         const size_t o = (size_t)t * p.ldy + row;
-        if (p.out_mode == GV_PUSH_F32) {
-            for (int pr = 0; pr < p.ar_out.tp; ++pr) p.ar_out.peer_buf[pr][((size_t)p.ar_out.rank * NT + t) * N + row] = v0;
-        } else if (p.out_mode == GV_STORE_F16) reinterpret_cast<__half*>(p.y)[o] = __float2half_rn(v0);
+        if (p.out_mode == GV_STORE_F16) reinterpret_cast<__half*>(p.y)[o] = __float2half_rn(v0);
         else if (p.out_mode == GV_STORE_F32) reinterpret_cast<float*>(p.y)[o] = v0;
         else if (p.out_mode == GV_ADD_F32) reinterpret_cast<float*>(p.y)[o] += v0;
         else reinterpret_cast<__half*>(p.y)[o] = __float2half_rn(gv_silu(v0) * v1);
     }
-    if (p.out_mode == GV_PUSH_F32) ar_signal(p.ar_out);
 }
 
 template <typename Kern>
@@ -964,11 +1024,15 @@ static int launch_gemv_qv3(Kern kern, const GemvParams& p, size_t x_smem, cudaSt
     const int groups = (p.w0.N + rpu - 1) / rpu;
     int blocks = sm_count() * 2;
     if (blocks > groups) blocks = groups;
+    const unsigned cl = ar_cluster(p, blocks);
     const int K = p.w0.K, KC = ((K / chunk_w) + 31) >> 5;
+    const size_t fixed = ((x_smem + 15) & ~size_t(15)) + (size_t)p.T * (K + (K >> 5) * 4 + (K >> 4) * 8);
+    blocks = resident_cluster_blocks(kern, cl, fixed + 4096, 256, blocks);
+    blocks -= blocks % (int)cl;
     const int max_groups = (groups + blocks - 1) / blocks + 1;
-    const size_t smem = ((x_smem + 15) & ~size_t(15)) + (size_t)p.T * (K + (K >> 5) * 4 + (K >> 4) * 8) + (size_t)max_groups * KC * 2 * p.T * sizeof(float);
+    const size_t smem = fixed + (size_t)max_groups * KC * 2 * p.T * sizeof(float);
     if (smem > 100 * 1024) return -2;   // caller falls back to v1
-    DLP_CHECK_CUDA(launch_pdl(kern, dim3(blocks), dim3(256), smem, stream, p));
+    DLP_CHECK_CUDA(launch_pdl_cluster(kern, dim3(blocks), dim3(256), smem, stream, cl, p));
     return 0;
 }
 
@@ -1018,7 +1082,9 @@ static int launch_gemv(Kern kern, const GemvParams& p, size_t smem, cudaStream_t
     int blocks = (p.w0.N + rows_per_block - 1) / rows_per_block;
     const int max_blocks = sm_count() * 4;
     if (blocks > max_blocks) blocks = max_blocks;
-    DLP_CHECK_CUDA(launch_pdl(kern, dim3(blocks), dim3(256), smem, stream, p));
+    const unsigned cl = ar_cluster(p, blocks);
+    blocks -= blocks % (int)cl;      // (grid-stride rows: any block count covers N)
+    DLP_CHECK_CUDA(launch_pdl_cluster(kern, dim3(blocks), dim3(256), smem, stream, cl, p));
     return 0;
 }
 
@@ -1030,7 +1096,7 @@ int gemv(const GemvParams& p_in, int wtype, cudaStream_t stream) {
     DLP_REQUIRE(K % 256 == 0, "gemv: K=%d must be a multiple of 256", K);
     DLP_REQUIRE(N % 2 == 0, "gemv: N=%d must be even", N);
     DLP_REQUIRE(p.out_mode != GV_SWIGLU_F16 || p.w1.base != nullptr, "gemv: SwiGLU needs both gate and up weights");
-    size_t smem = (size_t)T * K * 2 + (p.ar_in.buf ? (size_t)K * 4 : 0);
+    size_t smem = (size_t)T * K * 2 + ar_stage_bytes(p.ar_in.buf != nullptr, T, K);
     DLP_REQUIRE(p.ar_in.buf == nullptr || p.norm_w != nullptr, "gemv: the fused all-reduce prologue needs the RMSNorm fusion");
     DLP_REQUIRE(p.out_mode != GV_PUSH_F32 || (p.ar_out.tp >= 1 && p.ar_out.tp <= 8), "gemv: bad tensor-parallel size");
     const bool quant_bias = (wtype == W_Q4_K || wtype == W_Q5_K);
@@ -1088,7 +1154,7 @@ int gemv(const GemvParams& p_in, int wtype, cudaStream_t stream) {
     static int use_qv3 = -1;
     if (use_qv3 < 0) { const char* e = getenv("DLP_GEMV_QV3"); use_qv3 = (e && e[0] == '0') ? 0 : 1; }
     if (use_qv3 && (wtype == W_Q8_0 || wtype == W_Q4_K || wtype == W_Q5_K || wtype == W_Q6_K)) {
-        const size_t xsm = (size_t)T * K * 2 + (p.ar_in.buf ? (size_t)K * 4 : 0);
+        const size_t xsm = (size_t)T * K * 2 + ar_stage_bytes(p.ar_in.buf != nullptr, T, K);
         int rc = -2;
 #define DLP_QV3(WT_)                                                                                       \
     case WT_:                                                                                              \

@@ -6,20 +6,34 @@ namespace dlp {
 
 enum GemvOut : int { GV_STORE_F16 = 0, GV_STORE_F32 = 1, GV_ADD_F32 = 2, GV_SWIGLU_F16 = 3, GV_PUSH_F32 = 4 };
 
-// Fused tensor-parallel all-reduce around the decode mat-vecs (see gemv.cu, comm.cu).
-struct ArIn {                 // consumer: h_out = h_in + sum over ranks of buf[r]
-    const float* buf;         // local reduce buffer [tp][T][K] fp32 (nullptr: no all-reduce to consume)
-    const uint32_t* flags;    // local [tp] epoch flags written by the peers
-    const int* epoch;         // device-resident step counter (same value on every rank)
+// Fused tensor-parallel all-reduce around the decode mat-vecs (see gemv.cu, comm.cu, tpcomm.cuh).
+// Every rank owns, per all-reduce site, a symmetric buffer  [2 parities][tp source ranks][AR_MAX_T token rows][K] fp32  that
+// all peers can store into (peer pointers, or one NVLS multicast alias that the switch replicates to every rank).  A value is
+// its own arrival signal: buffers are pre-filled with AR_EMPTY (the bit pattern of -0.0f, which a producer never stores), the
+// consumer spins on the data words themselves, and it re-arms the *other* parity of its site for the step after next.  No
+// flag, no system-scope fence, no counter: the latency of an all-reduce is one NVLink store.
+constexpr uint32_t AR_EMPTY = 0x80000000u;
+constexpr int AR_MAX_T = 4;
+struct ArIn {                 // consumer: h_out = h_in + sum over ranks of buf[parity][r]
+    float* buf;               // local buffer of this site (nullptr: no all-reduce to consume)
+    const int* epoch;         // device-resident step counter (same value on every rank); parity = epoch & 1
     float* h_out;             // where CTA 0 stores the updated residual stream
     int* error;               // set to 1 on wait timeout
     int tp;
 };
-struct ArOut {                // producer: push this rank's partial rows to every peer
-    float* peer_buf[8];       // peer_buf[p] = base of peer p's reduce buffer for this site
-    uint32_t* peer_flags[8];  // peer_flags[p] = base of peer p's flag array for this site
+struct ArOut {                // producer: store this rank's partial rows into every rank's buffer
+    float* peer_buf[8];       // peer_buf[p] = base of rank p's buffer for this site (own rank included)
+    float* mc_buf;            // multicast alias of the same buffer (one multimem.st reaches all ranks), or nullptr
     const int* epoch;
-    unsigned* done_counter;   // local, zero-initialised
+    int rank, tp;
+};
+// Token exchange for sharded greedy sampling: slots [2 parities][tp][AR_MAX_T] of uint64, 0 = empty.
+struct TokX {
+    unsigned long long* peer_slots[8];
+    unsigned long long* mc_slots;
+    unsigned long long* slots;      // local
+    const int* epoch;
+    int* error;
     int rank, tp;
 };
 
@@ -128,6 +142,8 @@ int attn_decode_rope(const AttnParams& p, const float* qkv, const float* inv_fre
 int advance_rope(int* seq_len, const int* active, int* pos, int* slot, int* kv_len, const int* block_table, int max_pages,
                  int page_size, int n, const float* inv_freq, int n_pairs, float2* rope_cs, cudaStream_t s);
 int ar_consume(const float* h_in, float* h_out, const ArIn& a, int K, int T, cudaStream_t s);
+int argmax_tp(const float* logits, int R, int V, int ld, int v0, const TokX& x, int* out, cudaStream_t s);
+int fill_u32(uint32_t* p, size_t n, uint32_t v, cudaStream_t s);
 int bump(int* ctr, cudaStream_t s);
 int attn_prefill(const __half* q, const __half* kc, const __half* vc, const int* bt_row, __half* out, int T, int pos0,
                  int Hq, int Hkv, int D, int page_size, cudaStream_t s);

@@ -114,16 +114,20 @@ class LlamaEngine:
         qkv_dim = (self.Hq + 2 * self.Hkv) * self.D
         self.h = torch.zeros(M, self.E, dtype=f32, device=dev)
         self.fused_tp = bool(getattr(self.comm, "fused", False)) and self.comm.tp_size > 1 and not cfg.is_moe
+        self.sp_ok = False
+        self._greedy_now = False
         if self.fused_tp:
             if not self.comm.ready:
                 self.comm.setup(self.E, 2 * len(weights.layer_range))
             self.hb = [self.h, torch.zeros(4, self.E, dtype=f32, device=dev)]   # ping-pong residual (decode rows only)
             self.cur, self.pending = 0, None
             tp = self.comm.tp_size
-            if not getattr(self.comm, "sp_ready", False):
-                self.comm.sp_setup(self.E, M)
-            self.h_sh = torch.zeros(M // tp + 2, self.E, dtype=f32, device=dev)   # token-sharded residual (SP prefill)
-            self.G = [self.comm.sp_tensor(g) for g in (0, 1)]                            # gather buffers as fp16 [Tmax, E] views
+            self.sp_ok = not getattr(self.comm, "no_sp", False)
+            if self.sp_ok:
+                if not getattr(self.comm, "sp_ready", False):
+                    self.comm.sp_setup(self.E, M)
+                self.h_sh = torch.zeros(M // tp + 2, self.E, dtype=f32, device=dev)   # token-sharded residual (SP prefill)
+                self.G = [self.comm.sp_tensor(g) for g in (0, 1)]                            # gather buffers as fp16 [Tmax, E] views
         self.delta = torch.zeros(M, self.E, dtype=f32, device=dev)
         self.xn = torch.zeros(M, self.E, dtype=f16, device=dev)
         self.qkv32 = torch.zeros(min(M, 4), qkv_dim, dtype=f32, device=dev)
@@ -533,13 +537,17 @@ class LlamaEngine:
         self.h[:T].copy_(full.view(Tp, E)[:T])
         return None
 
-    def _finish_fused(self, T: int):
-        """Fold the last pending all-reduce: into the lm_head prologue (last stage) or a stand-alone consumer."""
+    def _finish_fused(self, T: int, greedy: bool = False):
+        """Fold the last pending all-reduce: into the lm_head prologue (last stage) or a stand-alone consumer.  Greedy steps
+        finish with the sharded arg-max (8-byte candidates exchanged through symmetric memory) instead of a logits all-gather."""
         c, cfg = self.comm, self.cfg
         hin, hout = self.hb[self.cur], self.hb[1 - self.cur]
         if self.last_stage:
             c.gemv(self.w.lm_head, hin, ops.OUT_F32, T, out=self.logits[:T], norm_w=self.w.out_norm, eps=cfg.rms_eps,
                    ar_in=c.ar_in(self.pending, hout))
+            if greedy:
+                c.argmax_sharded(self.logits[:T], self.w.vocab_range[0], self.next_tok[:T])
+                return None
             return c.allgather_logits(self.logits[:T], self.w.vocab_range, cfg.vocab_size)
         c.consume(hin, hout, self.pending, T)
         if self.cur == 0:           # hand-off buffer for the next stage is always self.h
@@ -578,7 +586,7 @@ class LlamaEngine:
             slot = pages[(pos // self.page_size).long()] * self.page_size + pos % self.page_size
             self.pos[:T].copy_(pos, non_blocking=True)
             self.slot[:T].copy_(slot.to(torch.int32), non_blocking=True)
-            sp = self.fused_tp and T > 4
+            sp = self.sp_ok and T > 4
             if self.first_stage:
                 self.tokens[:T].copy_(tokens[c0:c0 + T], non_blocking=True)
                 if not sp:
@@ -650,7 +658,7 @@ class LlamaEngine:
         ops.advance(self.seq_len_dev, self.active, self.pos, self.slot, self.kv_len, self.kv.block_table, self.page_size, B,
                     inv_freq=self.inv_freq, rope_cs=self.rope_cs)
         fused = self.fused_tp and B in (1, 2, 4)
-        sp = self.fused_tp and B > 4
+        sp = self.sp_ok and B > 4
         if sp:   # batched decode in the sequence-parallel layout (embedding happens per token shard inside)
             self.tokens[:B].copy_(self.next_tok[:B])
             lg = self._forward_sp(B, self._attn_decode, None)
@@ -659,7 +667,9 @@ class LlamaEngine:
                 self._embed(B, self.next_tok[:B])  # input ids = previously sampled (or host-provided) tokens
             self._run_layers(B, self._attn_decode, fused)
         if fused:
-            lg = self._finish_fused(B)
+            lg = self._finish_fused(B, greedy=sample and self._greedy_now)
+            if sample and self._greedy_now:
+                return      # sharded arg-max already wrote next_tok on every rank
         if self.last_stage:
             if not fused and not sp:
                 lg = self._head(slice(0, B), B)
@@ -689,13 +699,17 @@ class LlamaEngine:
                                             next(iter(self.w.layers.values())).e_gate_s is not None)
         graphable = (use_graph and self.eval_callback is None and self.device.type == "cuda" and not moe_host
                      and not getattr(self.comm, "no_graph", False)
-                     and not (self.fused_tp and B > 4))   # SP path passes host-side epochs as kernel arguments
+                     and not (self.sp_ok and B > 4))   # SP path passes host-side epochs as kernel arguments
         self._onepass_now = self.attn_onepass and max(self.seqs[sid].length for sid in sids) + 1 >= self.attn_onepass_min
         if sample and self.last_stage:
             self._sync_sampling(sids)
+        # all rows greedy on the fused tensor-parallel path: sharded arg-max instead of gathering the logits (host-side fact, so
+        # it is part of the graph key; at most one extra graph per batch size)
+        self._greedy_now = bool(sample and self.last_stage and self.fused_tp and B in (1, 2, 4) and
+                                os.environ.get("DLP_TP_ARGMAX", "1") == "1" and all(self._samp_host[sid][3] <= 0 for sid in sids))
         if graphable:
             # only the batch size, the output kind and the attention variant shape the graph (sampler parameters are device data)
-            key = (B, sample, self._onepass_now)
+            key = (B, sample, self._onepass_now, self._greedy_now)
             g = self._graphs.pop(key, None)
             if g is None:
                 while len(self._graphs) + 2 > self.max_graphs:    # least recently used graphs go first
@@ -705,7 +719,7 @@ class LlamaEngine:
                 if self.attn_onepass:   # capture the other attention variant now as well: the switch at 64 keys must not stall
                     want = self._onepass_now
                     self._onepass_now = not want
-                    self._capture(B, sample, key[:2] + (not want,))
+                    self._capture(B, sample, key[:2] + (not want,) + key[3:])
                     self._onepass_now = want
                 g = self._capture(B, sample, key)
                 self._graphs.pop(key)

@@ -1,16 +1,20 @@
-"""Tensor-parallel communicator whose all-reduce lives *inside* the decode mat-vec kernels.
+"""Tensor-parallel communicator whose collectives live *inside* the kernels.
 
 North-star item: "the column->row GEMM pair fuses the collective into the kernel: GEMM -> reduce/all-reduce issues
-NVSwitch P2P stores from inside the kernel".  Decode (T <= 4) path:
+NVSwitch P2P or NVLS-multicast stores from inside the kernel".  Decode (T <= 4) path:
 
-    o_proj / down GEMV (row-parallel, K shard)  --epilogue-->  st.global of the partial rows into EVERY peer's
-                                                               reduce buffer + st.release.sys of an epoch flag
-    next GEMV (QKV / gate+up / lm_head)         <--prologue--  ld.acquire.sys on the tp flags, then
-                                                               h = h + sum_r partial[r] fused with RMSNorm
+    o_proj / down GEMV (row-parallel, K shard)  --epilogue-->  partial rows stored into EVERY rank's buffer of the site:
+                                                               one `multimem.st` on the NVLS multicast alias (the switch
+                                                               replicates it) or one peer store per rank
+    next GEMV (QKV / gate+up / lm_head)         <--prologue--  spins on the values themselves (a value is its own arrival
+                                                               signal), then h = h + sum_r partial[r] fused with RMSNorm
+    lm_head (vocab shard) -> dlp_argmax_tp                     sharded greedy sampling: 8-byte (value, id) words exchanged the
+                                                               same way; no logits all-gather
 
-so a layer needs no separate collective launch and no NCCL call.  Buffers are symmetric allocations mapped
-into every rank through CUDA IPC (`csrc/comm.cu`).  Larger token counts (prefill, big decode batches) use the
-NCCL path of :class:`NcclComm` - that path is also the A/B baseline the spec asks to keep.
+so a decode step under TP has no collective launch, no flag, no system-scope fence and no NCCL call.  Buffers are symmetric
+allocations: `torch.distributed._symmetric_memory` when it gives a multicast pointer (plumbing only - the stores are ours), else
+cudaMalloc + CUDA IPC (`csrc/comm.cu`).  Larger token counts (prefill, big decode batches) use the sequence-parallel GEMM path
+below; the NCCL path of :class:`NcclComm` is the A/B baseline the spec asks to keep.
 
 Reference counterpart: `ggml_cuda_op_mul_mat` broadcast + gather through a hub GPU (`ggml-cuda.cu:1451-1769`).
 """
@@ -27,14 +31,21 @@ from .comm import NcclComm
 MAX_T = 4  # token rows per site in the fused path
 
 
+AR_EMPTY = 0x80000000  # bit pattern of -0.0f: "not here yet" (csrc/kernels.cuh)
+
+
 class dlp_ar_in(C.Structure):
-    _fields_ = [("buf", C.c_void_p), ("flags", C.c_void_p), ("epoch", C.c_void_p), ("h_out", C.c_void_p),
+    _fields_ = [("buf", C.c_void_p), ("epoch", C.c_void_p), ("h_out", C.c_void_p),
                 ("error", C.c_void_p), ("tp", C.c_int32), ("reserved", C.c_int32)]
 
 
 class dlp_ar_out(C.Structure):
-    _fields_ = [("peer_buf", C.c_void_p * 8), ("peer_flags", C.c_void_p * 8), ("epoch", C.c_void_p),
-                ("done_counter", C.c_void_p), ("rank", C.c_int32), ("tp", C.c_int32)]
+    _fields_ = [("peer_buf", C.c_void_p * 8), ("mc_buf", C.c_void_p), ("epoch", C.c_void_p), ("rank", C.c_int32), ("tp", C.c_int32)]
+
+
+class dlp_tokx(C.Structure):
+    _fields_ = [("peer_slots", C.c_void_p * 8), ("mc_slots", C.c_void_p), ("slots", C.c_void_p), ("epoch", C.c_void_p),
+                ("error", C.c_void_p), ("rank", C.c_int32), ("tp", C.c_int32)]
 
 
 class dlp_gemm_coll(C.Structure):
@@ -85,44 +96,85 @@ class FusedComm(NcclComm):
         L.dlp_gemm_sp.argtypes = [W, W, vp, i32, vp, i32, i32, i32, C.POINTER(dlp_gemm_coll), vp]
         L.dlp_rs_norm_ag.restype = i32
         L.dlp_rs_norm_ag.argtypes = [C.POINTER(dlp_rs_norm_ag_desc), vp]
+        L.dlp_argmax_tp.restype = i32
+        L.dlp_argmax_tp.argtypes = [vp, i32, i32, i32, i32, C.POINTER(dlp_tokx), vp, vp]
+        L.dlp_fill_u32.restype = i32
+        L.dlp_fill_u32.argtypes = [vp, C.c_size_t, C.c_uint32, vp]
 
     # ---- set-up: one symmetric allocation per rank, handles exchanged over the process group --------------
-    def setup(self, n_embd: int, n_sites: int):
+    def _layout(self, n_embd: int, n_sites: int):
         tp = self.tp_size
         self.E, self.n_sites = n_embd, n_sites
-        self.buf_bytes = tp * MAX_T * n_embd * 4
-        self.site_stride = self.buf_bytes + 256          # reduce buffer + flag line
-        total = n_sites * self.site_stride
+        self.site_stride = 2 * tp * MAX_T * n_embd * 4          # [2 parities][tp][MAX_T][E] fp32
+        self.tok_off = n_sites * self.site_stride                # token exchange slots: uint64 [2][tp][MAX_T]
+        self.total_bytes = self.tok_off + ((2 * tp * MAX_T * 8 + 255) // 256) * 256
+
+    def _alloc_symmetric(self, nbytes: int):
+        """(local base, [peer bases], multicast base or 0).  torch's symmetric memory is tried first because it also binds an NVLS
+        multicast object when the fabric has one; cudaMalloc + CUDA IPC otherwise (DLP_SYMM=ipc forces it)."""
+        import os
+        tp = self.tp_size
+        if os.environ.get("DLP_SYMM", "auto") != "ipc":
+            try:
+                import torch.distributed._symmetric_memory as symm_mem
+                t = symm_mem.empty(nbytes, dtype=torch.uint8, device=self.device)
+                hdl = symm_mem.rendezvous(t, group=self.group)
+                peers = [int(p) for p in hdl.buffer_ptrs]
+                mc = int(getattr(hdl, "multicast_ptr", 0) or 0)
+                if len(peers) == tp and peers[self.tp_rank] == t.data_ptr():
+                    self._symm_keep = getattr(self, "_symm_keep", []) + [(t, hdl)]
+                    self.symm_backend = "symm_mem+nvls" if mc else "symm_mem"
+                    if os.environ.get("DLP_SYMM_MC", "1") == "0":
+                        mc = 0
+                    return t.data_ptr(), peers, mc
+            except Exception as e:  # noqa: BLE001 - any failure of the optional path falls back to IPC
+                self.symm_note = f"{type(e).__name__}: {e}"[:200]
         p = C.c_void_p()
-        _lib.check(self.lib.dlp_symm_alloc(total, C.byref(p)), "symm_alloc")
-        self.base = p.value
+        _lib.check(self.lib.dlp_symm_alloc(nbytes, C.byref(p)), "symm_alloc")
         handle = (C.c_char * 64)()
-        _lib.check(self.lib.dlp_ipc_export(self.base, handle), "ipc_export")
-        mine = bytes(handle)
+        _lib.check(self.lib.dlp_ipc_export(p.value, handle), "ipc_export")
         gathered: list = [None] * tp
-        dist.all_gather_object(gathered, mine, group=self.group)
-        self.peers = []
+        dist.all_gather_object(gathered, bytes(handle), group=self.group)
+        peers = []
         for r, h in enumerate(gathered):
             if r == self.tp_rank:
-                self.peers.append(self.base)
+                peers.append(p.value)
                 continue
             q = C.c_void_p()
-            hb = (C.c_char * 64).from_buffer_copy(h)
-            _lib.check(self.lib.dlp_ipc_import(hb, C.byref(q)), "ipc_import")
-            self.peers.append(q.value)
-        self.epoch = torch.zeros(1, dtype=torch.int32, device=self.device)
-        self.done = torch.zeros(1, dtype=torch.int32, device=self.device)
-        self.error = torch.zeros(1, dtype=torch.int32, device=self.device)
-        self._in: dict[int, dlp_ar_in] = {}
-        self._out: dict[int, dlp_ar_out] = {}
+            _lib.check(self.lib.dlp_ipc_import((C.c_char * 64).from_buffer_copy(h), C.byref(q)), "ipc_import")
+            peers.append(q.value)
+        self.symm_backend = "cuda-ipc"
+        return p.value, peers, 0
+
+    def setup(self, n_embd: int, n_sites: int):
+        self._layout(n_embd, n_sites)
+        if getattr(self, "emulated", False):
+            self._mem = torch.zeros(self.total_bytes, dtype=torch.uint8, device=self.device)
+            self.base, self.mc_base, self.symm_backend = self._mem.data_ptr(), 0, "emulated"
+            self.peers = [self.base] * self.tp_size      # ar_out()/tokx() shift each "peer" to its own slot
+            self._arm()
+            self.ready = True
+            return
+        self.base, self.peers, self.mc_base = self._alloc_symmetric(self.total_bytes)
+        self._arm()
         dist.barrier(group=self.group)
         self.ready = True
+
+    def _arm(self):
+        """Initial state: every all-reduce word "empty", token slots zero, epoch 0."""
+        st = torch.cuda.current_stream().cuda_stream
+        _lib.check(self.lib.dlp_fill_u32(self.base, self.tok_off // 4, AR_EMPTY, st), "fill")
+        _lib.check(self.lib.dlp_fill_u32(self.base + self.tok_off, (self.total_bytes - self.tok_off) // 4, 0, st), "fill")
+        self.epoch = torch.zeros(1, dtype=torch.int32, device=self.device)
+        self.error = torch.zeros(1, dtype=torch.int32, device=self.device)
+        self._in, self._out, self._tokx = {}, {}, None
+        torch.cuda.synchronize()
 
     @classmethod
     def make_virtual(cls, tp: int, n_embd: int, n_sites: int, device="cuda") -> list["FusedComm"]:
         """`tp` communicators that live on ONE device and point at each other's buffers directly - no IPC, no process
-        group.  Used to test the push / flag / consume protocol on a single GPU: the caller launches each phase for all
-        virtual ranks in turn, so every flag is already published when a consumer looks at it (kernels that wait on each
+        group.  Used to test the store / spin / re-arm protocol on a single GPU: the caller launches each phase for all
+        virtual ranks in turn, so every value is already there when a consumer looks for it (kernels that wait on each
         other must never be co-scheduled on one GPU)."""
         comms = []
         for r in range(tp):
@@ -130,20 +182,31 @@ class FusedComm(NcclComm):
             c.group, c.tp_size, c.tp_rank, c._gather_buf = None, tp, r, None
             c.grid, c.device, c.lib = None, torch.device(device), _lib.load()
             c._declare()
-            c.E, c.n_sites = n_embd, n_sites
-            c.buf_bytes = tp * MAX_T * n_embd * 4
-            c.site_stride = c.buf_bytes + 256
-            c._mem = torch.zeros(n_sites * c.site_stride, dtype=torch.uint8, device=device)
-            c.base = c._mem.data_ptr()
-            c.epoch = torch.zeros(1, dtype=torch.int32, device=device)
-            c.done = torch.zeros(1, dtype=torch.int32, device=device)
-            c.error = torch.zeros(1, dtype=torch.int32, device=device)
-            c._in, c._out = {}, {}
+            c._layout(n_embd, n_sites)
+            c._mem = torch.zeros(c.total_bytes, dtype=torch.uint8, device=device)
+            c.base, c.mc_base, c.symm_backend = c._mem.data_ptr(), 0, "virtual"
+            c._arm()
             c.ready = True
             comms.append(c)
         for c in comms:
             c.peers = [o.base for o in comms]
         return comms
+
+    @classmethod
+    def make_emulated(cls, tp: int, n_embd: int | None = None, n_sites: int | None = None, device="cuda") -> "FusedComm":
+        """Rank 0 of a `tp`-way group on ONE device with nobody else: its stores into "rank r's buffer" land in slot r of its own
+        buffer, so its consumers find tp (identical) partials and never wait.  The kernels, shard shapes, launch counts and
+        per-rank bytes are exactly those of a real tp-way step; only the NVLink hop is missing.  For per-rank timing and
+        profiling of the tensor-parallel decode step on a single GPU (bench.py --emulate-tp)."""
+        c = cls.__new__(cls)
+        c.group, c.tp_size, c.tp_rank, c._gather_buf = None, tp, 0, None
+        c.grid, c.device, c.lib = None, torch.device(device), _lib.load()
+        c._declare()
+        c.ready, c.emulated, c.no_sp = False, True, True
+        c.base, c.peers = None, []
+        if n_embd is not None and n_sites is not None:
+            c.setup(n_embd, n_sites)
+        return c
 
     @classmethod
     def make_virtual_sp(cls, tp: int, E: int, t_max: int, device="cuda") -> list["FusedComm"]:
@@ -162,8 +225,7 @@ class FusedComm(NcclComm):
         key = (site, h_out.data_ptr())
         d = self._in.get(key)
         if d is None:
-            b = self.base + site * self.site_stride
-            d = dlp_ar_in(b, b + self.buf_bytes, self.epoch.data_ptr(), h_out.data_ptr(), self.error.data_ptr(), self.tp_size, 0)
+            d = dlp_ar_in(self.base + site * self.site_stride, self.epoch.data_ptr(), h_out.data_ptr(), self.error.data_ptr(), self.tp_size, 0)
             self._in[key] = d
         return d
 
@@ -171,15 +233,36 @@ class FusedComm(NcclComm):
         d = self._out.get(site)
         if d is None:
             d = dlp_ar_out()
-            for r in range(self.tp_size):
-                b = self.peers[r] + site * self.site_stride
-                d.peer_buf[r] = b
-                d.peer_flags[r] = b + self.buf_bytes
+            emu = getattr(self, "emulated", False)
+            for r in range(self.tp_size):   # (emulation: "rank r" is slot r of our own buffer)
+                d.peer_buf[r] = self.peers[r] + site * self.site_stride + (r * MAX_T * self.E * 4 if emu else 0)
+            d.mc_buf = (self.mc_base + site * self.site_stride) if self.mc_base else None
             d.epoch = self.epoch.data_ptr()
-            d.done_counter = self.done.data_ptr()
             d.rank, d.tp = self.tp_rank, self.tp_size
             self._out[site] = d
         return d
+
+    def tokx(self) -> dlp_tokx:
+        if self._tokx is None:
+            d = dlp_tokx()
+            emu = getattr(self, "emulated", False)
+            for r in range(self.tp_size):
+                d.peer_slots[r] = self.peers[r] + self.tok_off + (r * MAX_T * 8 if emu else 0)
+            d.mc_slots = (self.mc_base + self.tok_off) if self.mc_base else None
+            d.slots = self.base + self.tok_off
+            d.epoch, d.error = self.epoch.data_ptr(), self.error.data_ptr()
+            d.rank, d.tp = self.tp_rank, self.tp_size
+            self._tokx = d
+        return self._tokx
+
+    def argmax_sharded(self, logits: torch.Tensor, v0: int, out: torch.Tensor) -> torch.Tensor:
+        """Global arg-max over vocabulary-sharded logits [B, V_local] (B <= 4): the same token id on every rank, in one launch."""
+        from ..ops import api as ops
+        B, V = logits.shape
+        _lib.check(self.lib.dlp_argmax_tp(logits.data_ptr(), B, V, logits.stride(0), v0, C.byref(self.tokx()), out.data_ptr(),
+                                          torch.cuda.current_stream().cuda_stream), "argmax_tp")
+        ops._count()
+        return out
 
     # ---- sequence-parallel prefill: GEMM -> reduce-scatter, all-gather -> GEMM ---------------------------------
     # Symmetric layout per rank:  G0 | G1 (gather buffers [Tmax, E] fp16)  R0 | R1 (reduce buffers [tp][Tmax/tp][E] fp32)
@@ -301,6 +384,17 @@ class FusedComm(NcclComm):
         _lib.check(self.lib.dlp_ar_consume(h_in.data_ptr(), h_out.data_ptr(), C.byref(d), self.E, T,
                                            torch.cuda.current_stream().cuda_stream), "ar_consume")
         ops._count()
+
+    # ---- single-device emulation of rank 0 (make_emulated): the NCCL-style entry points without a process group ----
+    def allreduce_delta(self, delta, il, which):
+        if getattr(self, "emulated", False):
+            return delta.mul_(self.tp_size)          # tp identical partials
+        return super().allreduce_delta(delta, il, which)
+
+    def allgather_logits(self, logits, vocab_range, vocab_size):
+        if getattr(self, "emulated", False):
+            return logits.repeat(1, self.tp_size)[:, :vocab_size]
+        return super().allgather_logits(logits, vocab_range, vocab_size)
 
     def check_error(self):
         if int(self.error.item()):

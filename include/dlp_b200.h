@@ -125,7 +125,11 @@ int dlp_attn_paged_fused(const void* q, const void* k_cache, const void* v_cache
  * K/V at position kv_len-1 of its sequence (page from the block table), attends over kv_len keys and writes `out` fp16
  * [nq, Hq*D].  The n_splits (1..16) KV splits of a (query, KV-head group) run as one thread-block cluster and combine
  * through distributed shared memory - no workspace.  kv_len counts the new token.  `rope_cs` (optional) is the step's
- * [nq][D/2] table of (cos, sin) pairs written by dlp_advance_rope; when NULL the kernel evaluates sincosf from inv_freq. */
+ * [nq][D/2] table of (cos, sin) pairs written by dlp_advance_rope; when NULL the kernel evaluates sincosf from inv_freq.
+ * Ordering: with programmatic dependent launch on, the kernel reads kv_len, the block table and the cached K/V rows of earlier
+ * positions BEFORE it waits for its predecessor; only `qkv` is read after the wait.  Those inputs must therefore not be produced
+ * by the launch immediately before this one when that launch is one of this library's PDL-aware kernels (in the decode step
+ * they come from dlp_advance_rope at the start of the step and from earlier steps). */
 int dlp_advance_rope(int32_t* seq_len, const int32_t* active, int32_t* pos, int32_t* slot, int32_t* kv_len,
                      const int32_t* block_table, int max_pages, int page_size, int n, const float* inv_freq, int n_pairs,
                      float* rope_cs, void* stream);
@@ -189,32 +193,49 @@ int dlp_moe_route(const float* logits, int T, int n_expert, int top_k, int32_t* 
 int dlp_gemv_moe(const dlp_weight* w0, const dlp_weight* w1, const void* x, const float* norm_w, float eps, void* y, int ldy,
                  int out_mode, const int32_t* expert_id_dev, int rows_per_expert, const float* out_scale_dev, void* stream);
 
-/* ---- tensor-parallel decode with the all-reduce fused into the mat-vecs (NVLink peer stores, no NCCL) ----
- * Each rank owns a reduce buffer [tp][T][E] fp32 and a flag array [tp] per all-reduce site, mapped by all peers
- * (dlp_symm_alloc + dlp_ipc_export / dlp_ipc_import).  A row-parallel mat-vec launched with out_mode
- * DLP_OUT_PUSH_F32 stores its partial rows into every peer's buffer and then publishes the epoch flag; the next
- * mat-vec (or dlp_ar_consume) launched with a dlp_ar_in waits for the tp flags and folds
- *   h_out = h_in + sum_r buf[r]     into its RMSNorm prologue.
- * `epoch` is a device-resident counter with the same value on every rank (dlp_bump once per forward pass).
+/* ---- tensor-parallel decode with the all-reduce fused into the mat-vecs (NVLink stores from inside the kernels, no NCCL) ----
+ * Each rank owns, per all-reduce site, a symmetric buffer [2 parities][tp][DLP_AR_MAX_T][E] fp32 that every rank can store into:
+ * through peer mappings (dlp_symm_alloc + dlp_ipc_export / dlp_ipc_import, or any symmetric-memory allocator) and, when the
+ * fabric offers NVLS, through one multicast alias of all ranks' buffers.  The buffers start filled with DLP_AR_EMPTY
+ * (dlp_fill_u32).  A row-parallel mat-vec launched with out_mode DLP_OUT_PUSH_F32 stores its partial rows into slot [rank] of
+ * every rank - `multimem.st` on the alias (one store, replicated by the switch) or one store per peer pointer; a value is its
+ * own arrival signal (a producer never stores the bit pattern of -0.0f), so there is no flag, fence or counter.  The next
+ * mat-vec (or dlp_ar_consume) launched with a dlp_ar_in spins on the values of the current parity, folds
+ *   h_out = h_in + sum_r buf[r]     into its RMSNorm prologue, and re-arms the other parity for the step after next.
+ * `epoch` is a device-resident counter with the same value on every rank (dlp_bump once per forward pass); parity = epoch & 1.
+ * Every rank must run the same sequence of sites each step; a peer that never stores shows up in `error` after ~9 s.
  * ref: the hub-and-spoke broadcast/gather around split matmuls (ggml-cuda/ggml-cuda.cu:1680-1744) - no reduce exists there. */
 enum { DLP_OUT_PUSH_F32 = 4 };
+#define DLP_AR_MAX_T 4
+#define DLP_AR_EMPTY 0x80000000u
 typedef struct dlp_ar_in {
-    const float* buf;        /* local reduce buffer of this site (NULL: nothing to consume) */
-    const uint32_t* flags;   /* local flags [tp] */
+    float* buf;              /* local buffer of this site (NULL: nothing to consume) */
     const int32_t* epoch;
     float* h_out;            /* updated residual stream (written by CTA 0) */
-    int32_t* error;          /* optional: set to 1 if a peer never signalled */
+    int32_t* error;          /* optional: set to 1 if a peer never delivered */
     int32_t tp;
     int32_t reserved;
 } dlp_ar_in;
 typedef struct dlp_ar_out {
-    float* peer_buf[8];      /* this site's reduce buffer on every rank (own rank included) */
-    uint32_t* peer_flags[8];
+    float* peer_buf[8];      /* this site's buffer on every rank (own rank included) */
+    float* mc_buf;           /* multicast alias of this site's buffer, or NULL (then peer_buf is used) */
     const int32_t* epoch;
-    uint32_t* done_counter;  /* local scratch counter, zero-initialised, shared by all sites */
     int32_t rank;
     int32_t tp;
 } dlp_ar_out;
+/* Sharded greedy sampling: `logits` [R, V] are this rank's vocabulary shard (global ids v0 .. v0+V); every rank ends up with the
+ * same global arg-max in out[R].  Slots: uint64 [2 parities][tp][DLP_AR_MAX_T], zero-initialised, symmetric like the buffers above. */
+typedef struct dlp_tokx {
+    void* peer_slots[8];
+    void* mc_slots;          /* multicast alias or NULL */
+    void* slots;             /* local */
+    const int32_t* epoch;
+    int32_t* error;
+    int32_t rank;
+    int32_t tp;
+} dlp_tokx;
+int dlp_argmax_tp(const float* logits, int R, int V, int ld, int v0, const dlp_tokx* x, int32_t* out, void* stream);
+int dlp_fill_u32(void* p, size_t n_words, uint32_t value, void* stream);
 int dlp_gemv_tp(const dlp_weight* w0, const dlp_weight* w1, const void* x, const float* norm_w, float eps, void* y,
                 int ldy, int out_mode, int T, const dlp_ar_in* ar_in, const dlp_ar_out* ar_out, void* stream);
 int dlp_ar_consume(const float* h_in, float* h_out, const dlp_ar_in* ar_in, int E, int T, void* stream);

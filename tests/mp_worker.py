@@ -25,6 +25,7 @@ def main():
     ap.add_argument("--device", default="cpu")
     ap.add_argument("--batch", type=int, default=1)
     ap.add_argument("--tol", type=float, default=1e-3)
+    ap.add_argument("--greedy", type=int, default=0, help="also generate this many tokens device-fed and compare with the teacher-forced arg-max")
     a = ap.parse_args()
     grid = init_grid(pp=a.pp, device=a.device, timeout_s=90)
     comm = None
@@ -65,8 +66,25 @@ def main():
             ref.advance(cache, 1)
             if grid.last_stage:
                 worst = max(worst, nmse(want, got[row]))
+    greedy_ok = True
+    if a.greedy and grid.pp == 1:
+        # device-fed generation (sampled on the device: sharded arg-max on the fused path) vs arg-max of teacher-forced logits
+        p = [1, 5, 9, 200, 33, 7, 8, 426, 17]
+        sid = eng.alloc_seq()
+        want = [int(eng.prefill(sid, p).argmax())]
+        for _ in range(a.greedy - 1):
+            want.append(int(eng.decode([sid], [want[-1]], sample=False)[0].argmax()))
+        eng.free_seq(sid)
+        got = eng.generate(p, a.greedy)
+        greedy_ok = got == want
+        if not greedy_ok:
+            print(f"rank {grid.rank}: greedy mismatch {got} != {want}")
     if comm is not None and getattr(comm, "fused", False):
         comm.check_error()
+        if grid.rank == 0:
+            print(f"symmetric memory: {comm.symm_backend}, multicast {'on' if comm.mc_base else 'off'} {getattr(comm, 'symm_note', '')}")
+    if not greedy_ok:
+        worst = 1.0
     res = torch.tensor([worst], dtype=torch.float64)
     if grid.world > 1:
         if grid.device.type == "cuda":

@@ -337,8 +337,9 @@ def test_advance_bookkeeping():
 @pytest.mark.parametrize("t", [GGMLType.F16, GGMLType.Q8_0, GGMLType.Q4_K])
 @pytest.mark.parametrize("T", [1, 2, 4])
 def test_fused_allreduce_protocol_virtual_ranks(t, T):
-    """Row-parallel GEMV -> push to every peer's reduce buffer + flag; next GEMV's prologue folds h += sum(partials)
-    into its RMSNorm.  Four virtual ranks on one GPU, phases launched rank by rank (no co-scheduled waiting kernels)."""
+    """Row-parallel GEMV -> self-signalling stores into every rank's buffer; next GEMV's prologue spins on the values, folds
+    h += sum(partials) into its RMSNorm and re-arms the other parity.  Four virtual ranks on one GPU, phases launched rank by
+    rank (no co-scheduled waiting kernels); five steps so that both parities are reused after being re-armed."""
     from distributed_llm_pipeline_b200.parallel.fused import FusedComm
     tp, E, F = 4, 512, 1024
     comms = FusedComm.make_virtual(tp, E, n_sites=2)
@@ -354,7 +355,7 @@ def test_fused_allreduce_protocol_virtual_ranks(t, T):
     from distributed_llm_pipeline_b200.gguf.quants import dequantize, quantize
     import numpy as np
     deq = lambda m: torch.from_numpy(dequantize(quantize(m.numpy(), t), t, tuple(m.shape)).astype(np.float32)).to(DEV)
-    for step in range(2):                                       # two epochs through the same site: no stale flags / data
+    for step in range(5):                                       # several epochs through the same site: no stale data
         for c in comms:
             c.begin_step()
         for r, c in enumerate(comms):                           # phase 1: every rank pushes its partial rows
@@ -371,6 +372,82 @@ def test_fused_allreduce_protocol_virtual_ranks(t, T):
             assert nmse(y_ref, y) < (3e-4 if t.name.startswith("Q") else 2e-5)
             c.check_error()
         act = (act.float() * 0.5 + 0.1).half()
+
+
+def test_fused_allreduce_passes_negative_zero_and_changing_batch():
+    """-0.0 is the "empty" pattern on the wire: a partial that is exactly -0.0 must arrive as +0.0, not hang the consumer; and a
+    step with fewer token rows after one with more must not see the stale rows (the whole site is re-armed)."""
+    from distributed_llm_pipeline_b200.parallel.fused import FusedComm
+    tp, E, F = 2, 256, 512
+    comms = FusedComm.make_virtual(tp, E, n_sites=1)
+    g = torch.Generator().manual_seed(5)
+    w_next = DeviceWeight.from_dense(torch.randn(64, E, generator=g) * 0.05, GGMLType.F16, DEV)
+    nw = torch.ones(E, device=DEV)
+    zero_w = [DeviceWeight.from_dense(torch.zeros(E, F // tp), GGMLType.F16, DEV) for _ in range(tp)]
+    for step, T in enumerate([4, 1, 4, 2, 1]):
+        act = -torch.ones(T, F // tp, dtype=torch.float16, device=DEV)       # (-1) * (+0) = -0.0 in every partial
+        h = torch.randn(T, E, generator=g).to(DEV)
+        for c in comms:
+            c.begin_step()
+        for r, c in enumerate(comms):
+            c.gemv(zero_w[r], act, 4, T, ar_out=c.ar_out(0))
+        for c in comms:
+            h_out = torch.zeros_like(h)
+            y = torch.empty(T, 64, device=DEV)
+            c.gemv(w_next, h, 1, T, out=y, norm_w=nw, eps=1e-5, ar_in=c.ar_in(0, h_out))
+            torch.cuda.synchronize()
+            c.check_error()
+            assert torch.equal(h_out, h), step
+
+
+def test_sharded_argmax_emulated_rank():
+    """dlp_argmax_tp on the single-device emulation (rank 0's stores land in every slot of its own buffer): picks the shard's
+    best entry, lowest id on ties, offset by the shard's first global id; slots are re-armed across steps."""
+    from distributed_llm_pipeline_b200.parallel.fused import FusedComm
+    c = FusedComm.make_emulated(4, 256, 1)
+    g = torch.Generator().manual_seed(9)
+    for step in range(5):
+        B, V, v0 = [1, 2, 4, 1, 4][step], 4099, 1000
+        lg = torch.randn(B, V, generator=g).to(DEV)
+        lg[0, 77] = lg[0, 300] = 50.0                      # tie: the lower id wins
+        out = torch.zeros(B, dtype=torch.int32, device=DEV)
+        c.begin_step()
+        c.argmax_sharded(lg, v0, out)
+        torch.cuda.synchronize()
+        c.check_error()
+        want = lg.argmax(-1) + v0
+        want[0] = 77 + v0
+        assert out.tolist() == want.tolist(), step
+
+
+def test_emulated_tp_engine_fused_equals_unfused(tmp_models):
+    """The single-device emulation of a tp-way rank (bench.py --emulate-tp): its fused decode step (stores + spin + sharded
+    arg-max inside a CUDA graph) must reproduce the unfused step of the same shard (separate all-reduce stand-in)."""
+    from distributed_llm_pipeline_b200.models.llama import LlamaEngine
+    from distributed_llm_pipeline_b200.models.weights import load_weights
+    from distributed_llm_pipeline_b200.parallel.fused import FusedComm
+    path = tmp_models[("tiny128", "F16")]
+    tp = 2
+    w = load_weights(path, "cuda", tp_rank=0, tp_size=tp)
+    fused = LlamaEngine(w, n_ctx=128, max_seqs=2, page_size=16, max_batch_tokens=32, comm=FusedComm.make_emulated(tp))
+    plain_comm = FusedComm.make_emulated(tp)
+    plain_comm.fused = False
+    plain = LlamaEngine(w, n_ctx=128, max_seqs=2, page_size=16, max_batch_tokens=32, comm=plain_comm)
+    assert fused.fused_tp and not plain.fused_tp
+    prompt = [1, 5, 9, 200, 33, 7, 8]
+    sa, sb = fused.alloc_seq(), plain.alloc_seq()
+    la, lb = fused.prefill(sa, prompt), plain.prefill(sb, prompt)
+    assert nmse(lb, la) < 1e-5
+    tok = int(lb.argmax())
+    want = [tok]
+    for _ in range(9):
+        lb = plain.decode([sb], [want[-1]], sample=False, use_graph=False)[0]
+        la = fused.decode([sa], [want[-1]], sample=False)[0]
+        assert nmse(lb, la) < 1e-4
+        want.append(int(lb.argmax()))
+    fused.free_seq(sa)
+    assert fused.generate(prompt, 10) == want            # device-fed tokens through the sharded arg-max
+    fused.comm.check_error()
 
 
 @pytest.mark.parametrize("t", [GGMLType.F16, GGMLType.Q8_0])

@@ -26,7 +26,8 @@ def _need(n):
 @pytest.mark.parametrize("batch", [1, 2, 3])
 def test_tp2_gpu(tmp_models, impl, batch):
     _need(2)
-    r = _torchrun(2, ["--model", tmp_models[("tiny128", "F16")], "--device", "cuda", "--impl", impl, "--batch", str(batch)], 29711 + batch)
+    r = _torchrun(2, ["--model", tmp_models[("tiny128", "F16")], "--device", "cuda", "--impl", impl, "--batch", str(batch), "--greedy", "12"],
+                  29711 + batch)
     assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
     assert "MP_RESULT" in r.stdout
 
@@ -34,6 +35,25 @@ def test_tp2_gpu(tmp_models, impl, batch):
 def test_tp2_fused_quantised(tmp_models):
     _need(2)
     r = _torchrun(2, ["--model", tmp_models[("tiny128", "Q4_K_M")], "--device", "cuda", "--impl", "fused"], 29721)
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
+
+
+@pytest.mark.parametrize("symm", ["ipc", "nomc"])
+def test_tp2_fused_other_transports(tmp_models, symm, monkeypatch):
+    """The same fused step over cudaMalloc + CUDA IPC peer pointers, and over symmetric memory with the multicast alias unused."""
+    _need(2)
+    if symm == "ipc":
+        monkeypatch.setenv("DLP_SYMM", "ipc")
+    else:
+        monkeypatch.setenv("DLP_SYMM_MC", "0")
+    r = _torchrun(2, ["--model", tmp_models[("tiny128", "F16")], "--device", "cuda", "--impl", "fused", "--batch", "2", "--greedy", "12"], 29725)
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
+
+
+@pytest.mark.parametrize("n", [4, 8])
+def test_tp_wide_fused_gpu(tmp_models, n):
+    _need(n)
+    r = _torchrun(n, ["--model", tmp_models[("tiny-tp8", "F16")], "--device", "cuda", "--impl", "fused", "--batch", "2", "--greedy", "12"], 29727 + n)
     assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
 
 
