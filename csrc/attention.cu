@@ -253,7 +253,7 @@ __global__ void __launch_bounds__(128) attn_decode_rope_kernel(const AttnParams 
     // dependent chain length -> page id -> K/V row runs under the predecessor's tail instead of after it.
     const int len = p.kv_len[qi];                      // keys visible to this query, the new token included
     const int n_old = len - 1;                         // ... of which this many are already in the cache
-    const int eff = min((int)gridDim.x, max(1, (len + 63) / 64));
+    const int eff = min((int)gridDim.x, max(1, (len + p.keys_per_split - 1) / p.keys_per_split));
     if (eff == 1 && split > 0) return;                 // uniform over the cluster: nobody waits on a barrier in that case
     const bool active = split < eff;
     const int per = (len + eff - 1) / eff;
@@ -276,6 +276,7 @@ __global__ void __launch_bounds__(128) attn_decode_rope_kernel(const AttnParams 
     const int t_first = begin + warp * 4;
     if (active && t_first < end_c) fetch(t_first, kr, vr);
     pdl_wait();
+    if (p.pdl_early) pdl_launch_dependents();
     trace_event(p.trace, TR_ATTN | TR_WAITED);
 
     if (active) {
@@ -526,6 +527,16 @@ int attn_decode_rope(const AttnParams& p_in, const float* qkv, const float* inv_
                      __half* vc_w, int D, int neox, float q_scale, cudaStream_t s) {
     AttnParams p = p_in;
     p.trace = trace_buffer();
+    static int early = -1, kps = 0;
+    if (early < 0) {
+        const char* e = getenv("DLP_PDL_EARLY");
+        early = (e && e[0] == '0') ? 0 : 1;
+        const char* k = getenv("DLP_ATTN_KEYS_PER_SPLIT");
+        kps = k ? atoi(k) : 32;
+        if (kps < 16) kps = 16;
+    }
+    p.pdl_early = early;
+    p.keys_per_split = kps;
     DLP_REQUIRE(inv_freq != nullptr || rope_cs != nullptr, "attn_decode_rope: need inv_freq or a (cos, sin) table");
     DLP_REQUIRE(p.nq > 0 && p.Hq % p.Hkv == 0, "attn_decode_rope: bad head configuration Hq=%d Hkv=%d", p.Hq, p.Hkv);
     DLP_REQUIRE(p.n_splits >= 1 && p.n_splits <= 16, "attn_decode_rope: cluster size %d outside 1..16", p.n_splits);

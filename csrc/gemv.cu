@@ -317,6 +317,8 @@ __global__ void __launch_bounds__(256, 2) gemv_dense_v3_kernel(const GemvParams 
     trace_event(p.trace, TR_GEMV | TR_BEGIN);
     trace_event_cta(p.trace, TR_BEGIN);
     pdl_wait();
+    if (p.pdl_early) pdl_launch_dependents();   // right after the wait: the successor's launch latency hides under our main loop,
+                                                // and "my predecessor is complete when my successor starts" still holds
     trace_event(p.trace, TR_GEMV | TR_WAITED);
     trace_event_cta(p.trace, TR_WAITED);
     if (dyn_rows) {
@@ -924,6 +926,7 @@ __global__ void __launch_bounds__(256, 2) gemv_quant_v3_kernel(const GemvParams 
     }
     if (threadIdx.x == 0) next_unit = 8 * DEPTH;
     pdl_wait();
+    if (p.pdl_early) pdl_launch_dependents();
     if (dyn_rows) {
         roff = (*p.row_off_dev) * p.row_off_mul;
 #pragma unroll
@@ -1091,6 +1094,9 @@ static int launch_gemv(Kern kern, const GemvParams& p, size_t smem, cudaStream_t
 int gemv(const GemvParams& p_in, int wtype, cudaStream_t stream) {
     GemvParams p = p_in;
     p.trace = trace_buffer();
+    static int early = -1;
+    if (early < 0) { const char* e = getenv("DLP_PDL_EARLY"); early = (e && e[0] == '0') ? 0 : 1; }
+    p.pdl_early = early && p.ar_in.buf == nullptr;   // (measured: no gain, slightly slower, on the cluster launches that fold an all-reduce)
     const int K = p.w0.K, N = p.w0.N, T = p.T;
     DLP_REQUIRE(T == 1 || T == 2 || T == 4, "gemv: T=%d unsupported (1, 2 or 4; use the tcgen05 GEMM above that)", T);
     DLP_REQUIRE(K % 256 == 0, "gemv: K=%d must be a multiple of 256", K);

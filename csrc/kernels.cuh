@@ -54,6 +54,7 @@ struct GemvParams {
     int row_off_mul;
     const float* out_scale_dev;
     unsigned long long* trace = nullptr;   // device timeline buffer (common.cuh trace_event), normally null
+    int pdl_early = 0;                     // trigger the dependent launch right after the dependency wait (default on, DLP_PDL_EARLY=0)
 };
 int moe_route(const float* logits, int T, int n_expert, int top_k, int* ids, float* w, cudaStream_t s);
 
@@ -104,6 +105,8 @@ struct AttnParams {
     int* counters;          // [nq, Hkv * groups] zero-initialised; non-null => the last split CTA combines in-kernel
     int nq, Hq, Hkv, max_pages, page_size, n_splits;
     unsigned long long* trace = nullptr;   // device timeline buffer, normally null
+    int pdl_early = 0;
+    int keys_per_split = 64;               // one-launch decode kernel: target keys per cluster member
 };
 
 int gemv(const GemvParams& p, int wtype, cudaStream_t stream);

@@ -576,6 +576,8 @@ class LlamaEngine:
         tokens = torch.as_tensor(tokens, dtype=torch.int32)
         n = tokens.numel()
         chunk = min(chunk or self.max_tokens, self.max_tokens)
+        if all_logits and self.sp_ok and n > 4:     # refuse before anything is appended to the cache
+            raise NotImplementedError("all_logits is not available on the sequence-parallel prefill path")
         outs = []
         for c0 in range(0, n, chunk):
             T = min(chunk, n - c0)

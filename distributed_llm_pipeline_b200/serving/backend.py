@@ -19,7 +19,7 @@ import socketserver
 import sys
 import threading
 
-from .orchestrator import build_service
+from .orchestrator import add_parallel_args, build_service, maybe_reexec, service_kwargs, stop_service
 from ..utils.args import lora_from_args
 from .sampler import SamplingParams
 from .scheduler import Request
@@ -151,8 +151,10 @@ def main(argv=None):
     ap.add_argument("--max-queue", type=int, default=0)
     ap.add_argument("--slot-save-path", default=None)
     ap.add_argument("--context-shift", action="store_true")
+    add_parallel_args(ap)
     a = ap.parse_args(argv)
-    sched, info, logs = build_service(a.model, a.device, a.ctx_size, a.parallel, a.batch_size, lora=lora_from_args(a))
+    maybe_reexec(a, "distributed_llm_pipeline_b200.serving.backend", argv)
+    sched, info, logs = build_service(a.model, a.device, a.ctx_size, a.parallel, a.batch_size, lora=lora_from_args(a), **service_kwargs(a))
     for l in logs:
         sys.stderr.write(l)
     sys.stderr.flush()
@@ -169,7 +171,7 @@ def main(argv=None):
     except KeyboardInterrupt:
         pass
     finally:
-        sched.stop()
+        stop_service(sched)
 
 
 if __name__ == "__main__":

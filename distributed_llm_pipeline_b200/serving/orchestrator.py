@@ -17,6 +17,7 @@ import asyncio
 import json
 import mimetypes
 import os
+import sys
 import time
 import uuid
 
@@ -653,9 +654,27 @@ class ModelRouter(Orchestrator):
                 self._unload(n)
 
 
+def add_parallel_args(ap):
+    """Flags that put a distributed engine behind the front-end (the reference: `llama-cli --rpc a,b -ngl 99` per request,
+    `orchestrator/src/main.rs:47-48`; `llama-server -sm layer|row -ts ...`, `common/arg.cpp:2310-2358`)."""
+    ap.add_argument("--tp", type=int, default=int(os.environ.get("DLP_ARG_TP", "1")), help="tensor-parallel ranks per pipeline stage")
+    ap.add_argument("--pp", type=int, default=int(os.environ.get("DLP_ARG_PP", "1")), help="pipeline stages (layer split)")
+    ap.add_argument("--tp-impl", default=os.environ.get("DLP_TP_IMPL", "fused"), choices=["fused", "nccl"],
+                    help="tensor-parallel collectives: fused into the kernels (NVLink stores) or NCCL")
+    ap.add_argument("-ts", "--tensor-split", default=None, help="relative layer share of each pipeline stage, e.g. 3,1")
+    ap.add_argument("--rpc", default=os.environ.get("DLP_ARG_RPC"), help="comma separated host:port list of dlp-worker stages (CPU layer split)")
+    ap.add_argument("--workers", type=int, default=0, help="launch this many local dlp-worker stages and use them (implies --rpc)")
+    ap.add_argument("--worker-base-port", type=int, default=50052)
+
+
 def build_service(model: str, device: str = "cuda", n_ctx: int = 2048, n_slots: int = 4, n_batch: int = 2048, page_size: int = 64,
-                  lora=None):
-    """Load a GGUF checkpoint and return (scheduler, model_info, startup_logs)."""
+                  lora=None, pp: int = 1, tp: int = 1, tp_impl: str = "fused", tensor_split=None, rpc: str | None = None,
+                  workers: int = 0, worker_base_port: int = 50052):
+    """Load a GGUF checkpoint and return (scheduler, model_info, startup_logs).
+
+    pp * tp > 1: must run under torchrun (one process per rank); only the leader rank returns - followers replay the leader's
+    engine calls inside this function until the service shuts down and then exit (parallel/spmd.py).
+    rpc / workers: the engine is a chain of dlp-worker CPU stages driven over TCP (parallel/rpc.py)."""
     import torch
 
     from ..gguf import open_gguf
@@ -664,22 +683,87 @@ def build_service(model: str, device: str = "cuda", n_ctx: int = 2048, n_slots: 
     from ..utils.tokenizer import Tokenizer
     dev = device if (device != "cuda" or torch.cuda.is_available()) else "cpu"
     f = open_gguf(model)
-    t0 = time.time()
-    w = load_weights(f, dev, lora=lora)
-    eng = LlamaEngine(w, n_ctx=n_ctx, max_seqs=n_slots + 1, page_size=page_size if dev != "cpu" else 16, max_batch_tokens=n_batch)
     tok = Tokenizer(f.metadata)
-    cfg = w.cfg
-    logs = [
-        f"load: {os.path.basename(model)} | arch {cfg.arch} | {cfg.n_layer} layers | n_embd {cfg.n_embd} | vocab {cfg.vocab_size}\n",
-        f"load_tensors: offloaded {cfg.n_layer + 1}/{cfg.n_layer + 1} layers to GPU ({dev}), {w.nbytes() / 2**20:.1f} MiB in {time.time() - t0:.2f} s\n",
-        f"kv cache: {eng.kv.n_pages} pages x {eng.page_size} tokens ({eng.kv.bytes() / 2**20:.1f} MiB), {n_slots} slots, n_ctx {n_ctx}\n",
-    ]
+    t0 = time.time()
+    info_extra = {}
+    if workers or rpc:
+        from ..parallel.rpc import LocalWorkerPool, RpcEngine
+        pool = None
+        if workers:
+            pool = LocalWorkerPool(model, workers, base_port=worker_base_port, n_ctx=n_ctx)
+            rpc = ",".join(f"127.0.0.1:{worker_base_port + i}" for i in range(workers))
+        eng = RpcEngine(rpc.split(","), n_ctx=n_ctx, max_seqs=n_slots, recover=pool is not None)
+        eng._pool = pool
+        from ..models.config import config_from_gguf
+        cfg = config_from_gguf(f.metadata, f.tensors)
+        logs = [f"load: {os.path.basename(model)} | arch {cfg.arch} | {cfg.n_layer} layers | n_embd {cfg.n_embd} | vocab {cfg.vocab_size}\n"]
+        logs += eng.describe()
+        logs.append(f"RPC pipeline: {len(eng.workers)} stages, n_ctx {eng.n_ctx}, {n_slots} slots, ready in {time.time() - t0:.2f} s\n")
+    elif pp * tp > 1:
+        from ..parallel import spmd
+        from ..parallel.grid import init_grid, shutdown
+        grid = init_grid(pp=pp, tp=tp, device=dev)
+        split = [float(x) for x in tensor_split.split(",")] if isinstance(tensor_split, str) and tensor_split else tensor_split
+        eng_local, stage, comm, load_s, ranges = spmd.build_engine(f, grid, n_ctx, n_slots + 1, n_batch, page_size if dev != "cpu" else 16,
+                                                                   tp_impl, lora, split)
+        cfg = eng_local.cfg
+        mine = (f"load_tensors: stage {grid.stage} tp-rank {grid.tp_rank}: offloaded layers [{ranges[grid.stage].start}, {ranges[grid.stage].stop}) of "
+                f"{cfg.n_layer} to GPU {grid.device} ({eng_local.w.nbytes() / 2**20:.1f} MiB in {load_s:.2f} s"
+                f"{', +embedding' if grid.first_stage else ''}{', +lm_head' if grid.last_stage else ''})\n")
+        lines = [None] * grid.world
+        torch.distributed.all_gather_object(lines, mine)
+        leader = spmd.leader_rank(pp, tp)
+        ch = spmd.make_channel(grid, leader)
+        if grid.rank != leader:
+            spmd.follower_loop(eng_local, grid, stage, ch, log=sys.stderr.write)
+            shutdown(0)
+        eng = spmd.DistributedEngine(eng_local, grid, stage, ch)
+        impl = "fused in-kernel collectives" if getattr(comm, "fused", False) else ("NCCL / gloo collectives" if tp > 1 else "none")
+        logs = [f"load: {os.path.basename(model)} | arch {cfg.arch} | {cfg.n_layer} layers | n_embd {cfg.n_embd} | vocab {cfg.vocab_size}\n",
+                f"grid: {pp} pipeline stage(s) x {tp} tensor-parallel rank(s) = {grid.world} processes | TP: {impl}"
+                f"{' (' + comm.symm_backend + ')' if getattr(comm, 'symm_backend', None) else ''} | control: {os.environ.get('DLP_CTRL', 'shm')}\n"]
+        logs += lines
+        logs.append(f"kv cache: {eng_local.kv.n_pages} pages x {eng_local.page_size} tokens per rank ({eng_local.kv.bytes() / 2**20:.1f} MiB), {n_slots} slots, n_ctx {n_ctx}\n")
+        info_extra = {"pp": pp, "tp": tp}
+    else:
+        w = load_weights(f, dev, lora=lora)
+        eng = LlamaEngine(w, n_ctx=n_ctx, max_seqs=n_slots + 1, page_size=page_size if dev != "cpu" else 16, max_batch_tokens=n_batch)
+        cfg = w.cfg
+        logs = [
+            f"load: {os.path.basename(model)} | arch {cfg.arch} | {cfg.n_layer} layers | n_embd {cfg.n_embd} | vocab {cfg.vocab_size}\n",
+            f"load_tensors: offloaded {cfg.n_layer + 1}/{cfg.n_layer + 1} layers to GPU ({dev}), {w.nbytes() / 2**20:.1f} MiB in {time.time() - t0:.2f} s\n",
+            f"kv cache: {eng.kv.n_pages} pages x {eng.page_size} tokens ({eng.kv.bytes() / 2**20:.1f} MiB), {n_slots} slots, n_ctx {n_ctx}\n",
+        ]
     info = {"name": str(f.metadata.get("general.name", os.path.basename(model))), "n_params": cfg.n_params(), "n_ctx_train": cfg.n_ctx_train,
             "metadata": {"tokenizer.chat_template": f.metadata.get("tokenizer.chat_template", ""),
                          "bos_token": tok.tokens[tok.bos_id] if 0 <= tok.bos_id < tok.n_vocab else "",
-                         "eos_token": tok.tokens[tok.eos_id] if 0 <= tok.eos_id < tok.n_vocab else ""}}
+                         "eos_token": tok.tokens[tok.eos_id] if 0 <= tok.eos_id < tok.n_vocab else ""}, **info_extra}
     sched = Scheduler(eng, tok, n_batch=n_batch, n_slots=n_slots)
     return sched, info, logs
+
+
+def service_kwargs(a) -> dict:
+    return dict(pp=a.pp, tp=a.tp, tp_impl=a.tp_impl, tensor_split=a.tensor_split, rpc=a.rpc, workers=a.workers,
+                worker_base_port=a.worker_base_port)
+
+
+def maybe_reexec(a, module: str, argv):
+    """`--tp/--pp` outside torchrun: start the same command once per rank."""
+    if a.pp * a.tp > 1 and "WORLD_SIZE" not in os.environ and not (a.rpc or a.workers):
+        from ..parallel.spmd import reexec_under_torchrun
+        reexec_under_torchrun(a.pp * a.tp, list(sys.argv[1:] if argv is None else argv), module=module)
+
+
+def stop_service(sched):
+    sched.stop()
+    eng = sched.eng
+    if hasattr(eng, "shutdown"):          # distributed engine: release the followers
+        eng.shutdown()
+        from ..parallel.grid import shutdown
+        shutdown(0)
+    pool = getattr(eng, "_pool", None)
+    if pool is not None:
+        pool.stop()
 
 
 def main(argv=None):
@@ -701,7 +785,9 @@ def main(argv=None):
     ap.add_argument("--max-queue", type=int, default=0, help="answer 503 once this many requests are waiting (0 = unbounded)")
     ap.add_argument("--slot-save-path", default=None, help="directory for /slots/{id}?action=save|restore files")
     ap.add_argument("--context-shift", action="store_true", help="slide the context window instead of stopping at n_ctx")
+    add_parallel_args(ap)
     a = ap.parse_args(argv)
+    maybe_reexec(a, "distributed_llm_pipeline_b200.serving.orchestrator", argv)
     if a.models:
         if os.path.isdir(a.models):
             models = {os.path.splitext(f)[0]: os.path.join(a.models, f) for f in sorted(os.listdir(a.models)) if f.endswith(".gguf")}
@@ -717,7 +803,9 @@ def main(argv=None):
         return
     if not a.model:
         ap.error("-m/--model or --models is required")
-    sched, info, logs = build_service(a.model, a.device, a.ctx_size, a.parallel, a.batch_size, lora=lora_from_args(a))
+    sched, info, logs = build_service(a.model, a.device, a.ctx_size, a.parallel, a.batch_size, lora=lora_from_args(a), **service_kwargs(a))
+    for l in logs:
+        sys.stderr.write(l)
     sched.context_shift = a.context_shift
     sched.start()
     orch = Orchestrator(sched, info, a.static, a.predict, logs, api_key=a.api_key, max_queue=a.max_queue, slot_save_path=a.slot_save_path)
@@ -727,7 +815,7 @@ def main(argv=None):
     except KeyboardInterrupt:
         pass
     finally:
-        sched.stop()
+        stop_service(sched)
 
 
 if __name__ == "__main__":

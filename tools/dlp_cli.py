@@ -32,7 +32,21 @@ def main(argv=None):
     from distributed_llm_pipeline_b200.serving.scheduler import Request, Scheduler
     from distributed_llm_pipeline_b200.utils.tokenizer import Tokenizer
     t0 = time.time()
-    if a.rpc:
+    pp, tp = a.pp or 1, a.tp or 1
+    sched = None
+    if pp * tp > 1 and not a.rpc:
+        # a pp x tp grid of processes: this command re-starts itself under torchrun; the leader rank runs the conversation, the
+        # other ranks replay its engine calls (parallel/spmd.py) and leave inside build_service when the leader is done
+        if "WORLD_SIZE" not in os.environ:
+            from distributed_llm_pipeline_b200.parallel.spmd import reexec_under_torchrun
+            reexec_under_torchrun(pp * tp, list(sys.argv[1:] if argv is None else argv), script=os.path.abspath(__file__))
+        from distributed_llm_pipeline_b200.serving.orchestrator import build_service, stop_service
+        sched, _info, logs = build_service(a.model, a.device, a.ctx_size, a.parallel, min(a.batch_size, a.ubatch_size), lora=lora_from_args(a),
+                                           pp=pp, tp=tp, tp_impl=a.tp_impl, tensor_split=a.tensor_split)
+        for line in logs:
+            log.info(line.rstrip("\n"))
+        eng, tok = sched.eng, sched.tok
+    elif a.rpc:
         from distributed_llm_pipeline_b200.parallel.rpc import RpcEngine
         eng = RpcEngine(a.rpc.split(","), n_ctx=a.ctx_size, max_seqs=a.parallel)
         for line in eng.describe():
@@ -59,7 +73,7 @@ def main(argv=None):
         log.info(f"load_tensors: offloaded {w.cfg.n_layer + 1}/{w.cfg.n_layer + 1} layers to GPU ({dev}), {w.nbytes() / 2**20:.1f} MiB")
     log.info(f"model loaded in {time.time() - t0:.2f} s | n_ctx {a.ctx_size} | slots {a.parallel}")
     prompt = open(a.file).read() if a.file else a.prompt
-    if (a.model_draft or a.lookup) and not a.rpc:
+    if (a.model_draft or a.lookup) and not a.rpc and sched is None:
         # draft-and-verify generation (llama-speculative / llama-lookup): greedy, single sequence
         from distributed_llm_pipeline_b200.serving.speculative import ModelDrafter, NgramDrafter, SpecStats, generate_speculative
         if a.model_draft:
@@ -75,7 +89,8 @@ def main(argv=None):
                  f"drafted {st.n_drafted}, accepted {st.n_accepted} ({100 * st.acceptance:.1f}%), {st.n_generated / (time.time() - t1):.1f} tok/s")
         log.flush()
         return
-    sched = Scheduler(eng, tok, n_batch=a.batch_size)
+    if sched is None:
+        sched = Scheduler(eng, tok, n_batch=a.batch_size)
     sched.context_shift = a.context_shift
 
     def on_event(kind, content):
@@ -120,6 +135,8 @@ def main(argv=None):
             prompt = history + prompt
         last_prompt = prompt
     log.flush()
+    if pp * tp > 1 and not a.rpc:
+        stop_service(sched)
 
 
 if __name__ == "__main__":
