@@ -225,6 +225,44 @@ int dlp_linear(const dlp_weight* w0, const dlp_weight* w1, const void* x, const 
     return gemm_f16(scratch, up, w0->K, x, w0->K, y, ldy, T, w0->N, w0->K, epi, 0, 0, s);
 }
 
+int dlp_moe_route_ex(const float* logits, int ld, int T, int n_expert, int top_k, int renorm, int32_t* ids, float* weights, void* stream) {
+    DLP_REQUIRE(logits && ids && weights && T > 0 && ld >= n_expert, "dlp_moe_route_ex: bad argument");
+    return moe_route_ex(logits, ld, T, n_expert, top_k, renorm, ids, weights, (cudaStream_t)stream);
+}
+int dlp_moe_plan(const int32_t* ids, int n_assign, int n_expert, int token_tile, dlp_moe_plan_bufs* b, void* stream) {
+    DLP_REQUIRE(ids && b && b->pos && b->src && b->bounds && b->tile_expert && b->tile_row0 && b->tile_rows && b->n_tiles, "dlp_moe_plan: null argument");
+    return moe_plan(ids, n_assign, n_expert, token_tile, b->pos, b->src, b->bounds, b->tile_expert, b->tile_row0, b->tile_rows, b->n_tiles,
+                    (cudaStream_t)stream);
+}
+int dlp_moe_gather(const void* x, int ldx, const int32_t* src, int top_k, int n_assign, int K, void* xs, void* stream) {
+    DLP_REQUIRE(x && src && xs && n_assign > 0, "dlp_moe_gather: bad argument");
+    return moe_gather((const __half*)x, ldx, src, top_k, n_assign, K, (__half*)xs, (cudaStream_t)stream);
+}
+int dlp_moe_combine(const float* y, const int32_t* pos, const float* weights, int T, int top_k, int E, float* h, void* stream) {
+    DLP_REQUIRE(y && pos && weights && h, "dlp_moe_combine: null argument");
+    return moe_combine(y, pos, weights, T, top_k, E, h, (cudaStream_t)stream);
+}
+int dlp_linear_grouped(const dlp_weight* w0, const dlp_weight* w1, const void* xs, void* y, int ldy, int out_mode, int n_assign, int n_expert,
+                       int rows_per_expert, int token_tile, const dlp_moe_plan_bufs* b, void* stream) {
+    DLP_REQUIRE(w0 && w0->base && xs && y && b && b->tile_expert && n_assign > 0 && n_expert > 0, "dlp_linear_grouped: bad argument");
+    DLP_REQUIRE(out_mode == DLP_OUT_F16 || out_mode == DLP_OUT_F32 || out_mode == DLP_OUT_SWIGLU_F16, "dlp_linear_grouped: output mode %d", out_mode);
+    DLP_REQUIRE(w0->N == n_expert * rows_per_expert, "dlp_linear_grouped: weight has %d rows, expected %d x %d", w0->N, n_expert, rows_per_expert);
+    GemmGroup g;
+    g.tile_expert = b->tile_expert; g.tile_row0 = b->tile_row0; g.tile_rows = b->tile_rows; g.n_tiles = b->n_tiles;
+    g.rows_per_expert = rows_per_expert; g.n_expert = n_expert; g.bt = token_tile;
+    g.max_tiles = (n_assign + token_tile - 1) / token_tile + n_expert;     // every expert may end with one partial tile
+    const int epi = out_mode == DLP_OUT_F16 ? 0 : out_mode == DLP_OUT_F32 ? 1 : 3;
+    const int wt = w0->wtype;
+    cudaStream_t s = (cudaStream_t)stream;
+    if (wt == DLP_W_F16 || wt == DLP_W_BF16)
+        return gemm_f16(w0->base, w1 ? w1->base : nullptr, w0->K, xs, w0->K, y, ldy, n_assign, rows_per_expert, w0->K, epi, wt == DLP_W_BF16, 1, s,
+                        nullptr, &g);
+    const QWeight q0 = to_qw(w0);
+    QWeight q1;
+    if (w1) q1 = to_qw(w1);
+    return gemm_quant(q0, w1 ? &q1 : nullptr, wt, xs, w0->K, y, ldy, n_assign, epi, 1, s, nullptr, &g);
+}
+
 int dlp_dequant_rows_f32(const dlp_weight* w, const int32_t* row_ids, int n_rows, float* out, int ld_out, void* stream) {
     DLP_REQUIRE(w && w->base && out, "dlp_dequant_rows_f32: null argument");
     return dequant_rows_f32(to_qw(w), w->wtype, row_ids, n_rows, out, ld_out, (cudaStream_t)stream);

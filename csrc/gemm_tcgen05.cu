@@ -28,6 +28,7 @@ struct GemmParams {
     int epilogue;
     int k_blocks_per_split;
     GemmCollective coll;   // fused all-gather (X side) / reduce-scatter (Y side); zero-initialised = none
+    GemmGroup grp;         // grouped (MoE) launch: per-tile expert / row range table built on the device
 };
 
 template <int BT, int NA>
@@ -99,7 +100,7 @@ __device__ __forceinline__ void prefetch_row_slice(const QWeight& w, int row, in
 }
 
 template <int MODE, int CH>
-__device__ __forceinline__ void epi_loop(const GemmParams& p, const uint32_t (&r0)[CH], const uint32_t (&r1)[CH], int tb, int n) {
+__device__ __forceinline__ void epi_loop(const GemmParams& p, const uint32_t (&r0)[CH], const uint32_t (&r1)[CH], int tb, int n, int t_end) {
     if (MODE == EPI_RS_PUSH_F32) {
         // GEMM -> reduce-scatter: token t is owned by rank t / rs_rows; our partial for it goes straight into that rank's
         // reduce buffer, slot [our rank][t % rs_rows][n] (NVLink store).  Owner / local row advance incrementally.
@@ -108,7 +109,7 @@ __device__ __forceinline__ void epi_loop(const GemmParams& p, const uint32_t (&r
         float* dst = p.coll.rs_peer_buf[owner] + ((size_t)p.coll.rs_rank * p.coll.rs_rows + local) * p.N + n;
 #pragma unroll
         for (int j = 0; j < CH; ++j) {
-            if (tb + j < p.T) *dst = __uint_as_float(r0[j]);
+            if (tb + j < t_end) *dst = __uint_as_float(r0[j]);
             dst += p.N;
             if (++local == p.coll.rs_rows) {
                 local = 0;
@@ -121,7 +122,7 @@ __device__ __forceinline__ void epi_loop(const GemmParams& p, const uint32_t (&r
     size_t o = (size_t)tb * p.ldy + n;
 #pragma unroll
     for (int j = 0; j < CH; ++j, o += p.ldy) {
-        if (tb + j >= p.T) break;
+        if (tb + j >= t_end) break;
         const float v = __uint_as_float(r0[j]);
         if (MODE == EPI_STORE_F16) reinterpret_cast<__half*>(p.y)[o] = __float2half_rn(v);
         else if (MODE == EPI_STORE_BF16) reinterpret_cast<__nv_bfloat16*>(p.y)[o] = __float2bfloat16_rn(v);
@@ -152,8 +153,17 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tm_w0, const __grid_cons
 
     const int warp = threadIdx.x >> 5;
     const int lane = threadIdx.x & 31;
-    const int n0 = blockIdx.x * GEMM_BM;
-    const int t0 = blockIdx.y * BT;
+    int n0 = blockIdx.x * GEMM_BM;      // first weight row of this tile (A operand)
+    int t0 = blockIdx.y * BT;           // first token row (B operand, output row)
+    int t_end = p.T;                    // output rows >= t_end are not stored
+    const int n_out0 = n0;              // first output column
+    if (p.grp.tile_expert != nullptr) {
+        // grouped launch: this token tile belongs to one expert; its weight rows sit at expert * rows_per_expert in the stack
+        if ((int)blockIdx.y >= *p.grp.n_tiles) return;          // (uniform over the CTA, before any barrier / TMEM allocation)
+        n0 += p.grp.tile_expert[blockIdx.y] * p.grp.rows_per_expert;
+        t0 = p.grp.tile_row0[blockIdx.y];
+        t_end = t0 + p.grp.tile_rows[blockIdx.y];
+    }
     const int total_kb = p.K / GEMM_BK;
     const int kb_begin = blockIdx.z * p.k_blocks_per_split;
     const int kb_end = min(total_kb, kb_begin + p.k_blocks_per_split);
@@ -255,7 +265,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tm_w0, const __grid_cons
         }
         // ===== epilogue: 4 warps, warp%4 selects the TMEM lane quarter =====
         const int q = warp & 3;
-        const int n = n0 + q * 32 + lane;
+        const int n = n_out0 + q * 32 + lane;
         if (num_kb > 0) {
             mbar_wait(tmem_full_bar, 0);
             tc_fence_after();
@@ -264,7 +274,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tm_w0, const __grid_cons
         constexpr int CH = BT >= 32 ? 32 : 16;
 #pragma unroll 1
         for (int c = 0; c < BT / CH; ++c) {
-            if (t0 + c * CH >= p.T) break;  // warp-uniform
+            if (t0 + c * CH >= t_end) break;  // warp-uniform
             uint32_t r0[CH], r1[CH];
             if (num_kb > 0) {
                 if constexpr (CH == 32) {
@@ -284,12 +294,12 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tm_w0, const __grid_cons
                 // reduce-scatter address arithmetic inside it cost 35-50 % of the whole GEMM, see profiles/r1_gemm_ab.txt)
                 const int tb = t0 + c * CH;
                 switch (p.epilogue) {
-                    case EPI_STORE_F16: epi_loop<EPI_STORE_F16, CH>(p, r0, r1, tb, n); break;
-                    case EPI_STORE_BF16: epi_loop<EPI_STORE_BF16, CH>(p, r0, r1, tb, n); break;
-                    case EPI_STORE_F32: epi_loop<EPI_STORE_F32, CH>(p, r0, r1, tb, n); break;
-                    case EPI_ATOMIC_ADD_F32: epi_loop<EPI_ATOMIC_ADD_F32, CH>(p, r0, r1, tb, n); break;
-                    case EPI_SWIGLU_F16: if (NA == 2) epi_loop<EPI_SWIGLU_F16, CH>(p, r0, r1, tb, n); break;
-                    case EPI_RS_PUSH_F32: epi_loop<EPI_RS_PUSH_F32, CH>(p, r0, r1, tb, n); break;
+                    case EPI_STORE_F16: epi_loop<EPI_STORE_F16, CH>(p, r0, r1, tb, n, t_end); break;
+                    case EPI_STORE_BF16: epi_loop<EPI_STORE_BF16, CH>(p, r0, r1, tb, n, t_end); break;
+                    case EPI_STORE_F32: epi_loop<EPI_STORE_F32, CH>(p, r0, r1, tb, n, t_end); break;
+                    case EPI_ATOMIC_ADD_F32: epi_loop<EPI_ATOMIC_ADD_F32, CH>(p, r0, r1, tb, n, t_end); break;
+                    case EPI_SWIGLU_F16: if (NA == 2) epi_loop<EPI_SWIGLU_F16, CH>(p, r0, r1, tb, n, t_end); break;
+                    case EPI_RS_PUSH_F32: epi_loop<EPI_RS_PUSH_F32, CH>(p, r0, r1, tb, n, t_end); break;
                 }
             }
         }
@@ -357,7 +367,7 @@ static int launch_gemm(const CUtensorMap& tw0, const CUtensorMap& tw1, const CUt
     auto kern = gemm_tcgen05_kernel<BT, NA, AB_FMT, WT>;
     if (first_use_on_device((const void*)kern))
         DLP_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES));
-    dim3 grid((p.N + GEMM_BM - 1) / GEMM_BM, (p.T + BT - 1) / BT, splits);
+    dim3 grid((p.N + GEMM_BM - 1) / GEMM_BM, p.grp.tile_expert ? p.grp.max_tiles : (p.T + BT - 1) / BT, splits);
     kern<<<grid, 192, Cfg::SMEM_BYTES, stream>>>(tw0, tw1, tx, p, qw0, qw1);
     DLP_LAUNCH_CHECK();
     return 0;
@@ -365,8 +375,11 @@ static int launch_gemm(const CUtensorMap& tw0, const CUtensorMap& tw1, const CUt
 
 // Y[T,N] (op)= X[T,K] . W0[N,K]^T  (and W1 for SwiGLU).  X/W are fp16 (is_bf16=0) or bf16 (is_bf16=1).
 int gemm_f16(const void* w0, const void* w1, int ldw, const void* x, int ldx, void* y, int ldy, int T, int N, int K,
-             int epilogue, int is_bf16, int split_k, cudaStream_t stream, const GemmCollective* coll) {
+             int epilogue, int is_bf16, int split_k, cudaStream_t stream, const GemmCollective* coll, const GemmGroup* grp) {
+    // grouped: N = output features of ONE expert, w0/w1 = stacks of all experts (rows_total = what the tensor map must cover)
     DLP_REQUIRE(T > 0 && N > 0 && K > 0, "gemm: empty problem T=%d N=%d K=%d", T, N, K);
+    DLP_REQUIRE(grp == nullptr || (grp->tile_expert && grp->tile_row0 && grp->tile_rows && grp->n_tiles && grp->max_tiles > 0 && split_k <= 1 &&
+                                   epilogue != EPI_RS_PUSH_F32 && epilogue != EPI_ATOMIC_ADD_F32), "gemm: bad grouped descriptor");
     DLP_REQUIRE(K % GEMM_BK == 0, "gemm: K=%d must be a multiple of %d", K, GEMM_BK);
     const int na = (epilogue == EPI_SWIGLU_F16) ? 2 : 1;
     DLP_REQUIRE(na == 1 || w1 != nullptr, "gemm: SwiGLU epilogue needs the up-projection weight");
@@ -391,13 +404,16 @@ int gemm_f16(const void* w0, const void* w1, int ldw, const void* x, int ldx, vo
     p.y = y; p.T = T; p.N = N; p.K = K; p.ldy = ldy; p.epilogue = epilogue;
     p.k_blocks_per_split = (total_kb + splits - 1) / splits;
     splits = (total_kb + p.k_blocks_per_split - 1) / p.k_blocks_per_split;
+    if (grp) p.grp = *grp;
 
-    const int bt = T <= 16 ? 16 : T <= 32 ? 32 : T <= 64 ? 64 : T <= 128 ? 128 : 256;
+    const int bt = grp ? grp->bt : (T <= 16 ? 16 : T <= 32 ? 32 : T <= 64 ? 64 : T <= 128 ? 128 : 256);
+    DLP_REQUIRE(bt == 16 || bt == 32 || bt == 64 || bt == 128 || bt == 256, "gemm: token tile %d", bt);
+    const uint64_t w_rows = grp ? (uint64_t)grp->rows_per_expert * grp->n_expert : (uint64_t)N;   // grouped: the map spans the whole stack
     CUtensorMap tw0, tw1, tx;
     int rc;
-    if ((rc = make_tmap_2d(&tw0, w0, is_bf16, N, K, ldw, GEMM_BM))) return rc;
+    if ((rc = make_tmap_2d(&tw0, w0, is_bf16, w_rows, K, ldw, GEMM_BM))) return rc;
     tw1 = tw0;
-    if (na == 2 && (rc = make_tmap_2d(&tw1, w1, is_bf16, N, K, ldw, GEMM_BM))) return rc;
+    if (na == 2 && (rc = make_tmap_2d(&tw1, w1, is_bf16, w_rows, K, ldw, GEMM_BM))) return rc;
     if ((rc = make_tmap_2d(&tx, x, is_bf16, T, K, ldx, bt))) return rc;
 
 #define DLP_GEMM_CASE(BT_)                                                                         \
@@ -419,9 +435,13 @@ int gemm_f16(const void* w0, const void* w1, int ldw, const void* x, int ldx, vo
 
 // Y[T,N] (op)= X[T,K] . dequant(W)[N,K]^T with the block-quant decode fused into the A-operand producer.
 int gemm_quant(const QWeight& w0, const QWeight* w1, int wtype, const void* x, int ldx, void* y, int ldy, int T, int epilogue,
-               int split_k, cudaStream_t stream, const GemmCollective* coll) {
-    const int N = w0.N, K = w0.K;
+               int split_k, cudaStream_t stream, const GemmCollective* coll, const GemmGroup* grp) {
+    // grouped: w0 / w1 describe the stack of all experts (w0.N = n_expert * rows_per_expert); one expert's width tiles the grid
+    const int N = grp ? grp->rows_per_expert : w0.N, K = w0.K;
     DLP_REQUIRE(T > 0 && N > 0 && K > 0 && K % 256 == 0, "gemm_quant: bad problem T=%d N=%d K=%d", T, N, K);
+    DLP_REQUIRE(grp == nullptr || (grp->tile_expert && grp->tile_row0 && grp->tile_rows && grp->n_tiles && grp->max_tiles > 0 && split_k <= 1 &&
+                                   epilogue != EPI_RS_PUSH_F32 && epilogue != EPI_ATOMIC_ADD_F32 && w0.N == grp->rows_per_expert * grp->n_expert),
+                "gemm_quant: bad grouped descriptor");
     const int na = (epilogue == EPI_SWIGLU_F16) ? 2 : 1;
     DLP_REQUIRE(na == 1 || w1 != nullptr, "gemm_quant: SwiGLU epilogue needs the up-projection weight");
     const int total_kb = K / GEMM_BK;
@@ -445,7 +465,8 @@ int gemm_quant(const QWeight& w0, const QWeight* w1, int wtype, const void* x, i
     p.y = y; p.T = T; p.N = N; p.K = K; p.ldy = ldy; p.epilogue = epilogue;
     p.k_blocks_per_split = (total_kb + splits - 1) / splits;
     splits = (total_kb + p.k_blocks_per_split - 1) / p.k_blocks_per_split;
-    const int bt = T <= 16 ? 16 : T <= 32 ? 32 : T <= 64 ? 64 : T <= 128 ? 128 : 256;
+    if (grp) p.grp = *grp;
+    const int bt = grp ? grp->bt : (T <= 16 ? 16 : T <= 32 ? 32 : T <= 64 ? 64 : T <= 128 ? 128 : 256);
     CUtensorMap tx;
     int rc;
     if ((rc = make_tmap_2d(&tx, x, 0, T, K, ldx, bt))) return rc;

@@ -109,11 +109,33 @@ struct AttnParams {
     int keys_per_split = 64;               // one-launch decode kernel: target keys per cluster member
 };
 
+// Grouped (mixture-of-experts) form of the tcgen05 GEMM: the X rows are the expert-sorted token copies, the weight is the stack of
+// all experts' matrices, and token tile j of the launch (blockIdx.y) belongs to expert tile_expert[j] and covers sorted rows
+// [tile_row0[j], tile_row0[j] + tile_rows[j]).  The table is built on the device (moe_plan), so the step never visits the host;
+// the launch uses an upper bound of tiles and surplus CTAs leave at once.
+struct GemmGroup {
+    const int* tile_expert = nullptr;   // nullptr: plain GEMM
+    const int* tile_row0 = nullptr;
+    const int* tile_rows = nullptr;
+    const int* n_tiles = nullptr;
+    int rows_per_expert = 0;            // output features of one expert (rows of the stacked weight per expert)
+    int n_expert = 0;
+    int max_tiles = 0;
+    int bt = 0;                         // token-tile size the table was built for
+};
+
 int gemv(const GemvParams& p, int wtype, cudaStream_t stream);
 int gemm_f16(const void* w0, const void* w1, int ldw, const void* x, int ldx, void* y, int ldy, int T, int N, int K,
-             int epilogue, int is_bf16, int split_k, cudaStream_t stream, const GemmCollective* coll = nullptr);
+             int epilogue, int is_bf16, int split_k, cudaStream_t stream, const GemmCollective* coll = nullptr,
+             const GemmGroup* grp = nullptr);
 int gemm_quant(const QWeight& w0, const QWeight* w1, int wtype, const void* x, int ldx, void* y, int ldy, int T, int epilogue,
-               int split_k, cudaStream_t stream, const GemmCollective* coll = nullptr);
+               int split_k, cudaStream_t stream, const GemmCollective* coll = nullptr, const GemmGroup* grp = nullptr);
+// MoE routing plan + data movement around the grouped GEMMs (moe.cu)
+int moe_route_ex(const float* logits, int ld, int T, int n_expert, int top_k, int renorm, int* ids, float* w, cudaStream_t s);
+int moe_plan(const int* ids, int n_assign, int n_expert, int bt, int* pos, int* src, int* bounds, int* tile_expert, int* tile_row0,
+             int* tile_rows, int* n_tiles, cudaStream_t s);
+int moe_gather(const __half* x, int ldx, const int* src, int top_k, int n_assign, int K, __half* xs, cudaStream_t s);
+int moe_combine(const float* y, const int* pos, const float* w, int T, int top_k, int E, float* h, cudaStream_t s);
 int dequant_rows_f32(const QWeight& w, int wtype, const int* row_ids, int n_rows, float* out, int ld_out, cudaStream_t s);
 int dequant_rows_f16(const QWeight& w, int wtype, const int* row_ids, int n_rows, __half* out, int ld_out, cudaStream_t s);
 int rmsnorm(float* h, const float* delta, const float* w, __half* out, int T, int E, float eps, cudaStream_t s);

@@ -359,8 +359,7 @@ class LlamaEngine:
         self.pending = 2 * li + 1
 
     def _moe(self, lw, T: int, xn):
-        """Top-k routed experts (softmax over all experts, top-k, renormalise: llama-graph.cpp:1039-1139).
-        Round-1 implementation: router + expert selection on the host side of the stream (not graph-capturable)."""
+        """Top-k routed experts (softmax over all experts, top-k, renormalise: llama-graph.cpp:1039-1139)."""
         cfg, comm = self.cfg, self.comm
         h = self.h[:T]
         if (T <= 4 and lw.e_gate_s is not None and cfg.n_expert <= 32 and cfg.n_embd % 256 == 0 and comm.tp_size == 1
@@ -368,6 +367,9 @@ class LlamaEngine:
             return self._moe_device(lw, T)
         if xn is None:
             xn = ops.rmsnorm(h, lw.ffn_norm, cfg.rms_eps, out=self.xn[:T])
+        if self._moe_grouped_ok(lw):
+            return self._moe_grouped(lw, T, xn)
+        # host-routed fallback (CPU engine, mixed expert types): not graph-capturable
         logits = xn.float() @ lw.router.T
         probs = torch.softmax(logits, -1)
         topw, topi = probs.topk(cfg.n_expert_used, -1)
@@ -389,6 +391,48 @@ class LlamaEngine:
         if comm.tp_size > 1:
             out = comm.allreduce_delta(out, -1, 1)
         h.add_(out)
+
+    def _moe_grouped_ok(self, lw) -> bool:
+        cfg = self.cfg
+        return (self.device.type == "cuda" and lw.e_gate_s is not None and lw.router_wp is not None and cfg.n_expert <= 256
+                and cfg.n_expert_used <= 32 and not ops.TWO_PASS_DEQUANT and os.environ.get("DLP_MOE_GROUPED", "1") == "1")
+
+    def _moe_grouped(self, lw, T: int, xn):
+        """Any token count, any MoE family, tp >= 1, entirely on the device (graph-capturable): router GEMM -> route -> plan
+        (expert-sorted order + token-tile table) -> gather -> ONE grouped tcgen05 GEMM per projection over all experts ->
+        weighted combine in slot order.  Under tensor parallelism every expert's n_ff is sharded like a dense FFN, so the
+        combine produces a partial sum that takes the usual all-reduce.  ref: mmid.cu + mul_mat_q ids path, topk-moe.cu."""
+        cfg, comm = self.cfg, self.comm
+        k, nE, E, F = cfg.n_expert_used, cfg.n_expert, self.E, self.F
+        A = T * k
+        if not hasattr(self, "moe_g"):
+            dev, M = self.device, self.max_tokens + 8
+            self.moe_g = dict(logits=torch.zeros(M, lw.router_wp.N, dtype=torch.float32, device=dev),
+                              ids=torch.zeros(M * k, dtype=torch.int32, device=dev), w=torch.zeros(M * k, dtype=torch.float32, device=dev),
+                              plan=ops.MoePlan(M * k, nE, dev), xs=torch.zeros(M * k, E, dtype=torch.float16, device=dev),
+                              act=torch.zeros(M * k, F, dtype=torch.float16, device=dev), y=torch.zeros(M * k, E, dtype=torch.float32, device=dev))
+        b = self.moe_g
+        h = self.h[:T]
+        ops.linear(lw.router_wp, xn, "f32", out=b["logits"][:T])     # router (padded to a full 128-row tile for the GEMM sizes)
+        ops.moe_route_ex(b["logits"][:T], nE, k, cfg.moe_norm_topk, b["ids"][:A], b["w"][:A])
+        per = max(1, A // nE)
+        bt = 16 if per <= 16 else 32 if per <= 32 else 64 if per <= 96 else 128
+        ops.moe_plan(b["ids"][:A], nE, bt, b["plan"])
+        ops.moe_gather(xn, b["plan"], k, A, b["xs"][:A])
+        ops.linear_grouped(lw.e_gate_s, b["xs"][:A], b["act"][:A], "swiglu", nE, F, bt, b["plan"], w_up=lw.e_up_s)
+        ops.linear_grouped(lw.e_down_s, b["act"][:A], b["y"][:A], "f32", nE, E, bt, b["plan"])
+        tp = comm.tp_size > 1
+        tgt = h
+        if tp:
+            tgt = self.delta[:T]
+            tgt.zero_()
+        ops.moe_combine(b["y"][:A], b["plan"], b["w"][:A], T, k, tgt)
+        if lw.shared_gate is not None:   # qwen2moe: always-on shared expert behind a sigmoid gate (device ops, no sync)
+            act = ops.linear(lw.w_gate, xn, "swiglu", w_up=lw.w_up)
+            ys = ops.linear(lw.w_down, act, "f32")
+            tgt.addcmul_(torch.sigmoid(xn.float() @ lw.shared_gate)[:, None], ys)
+        if tp:
+            h.add_(comm.allreduce_delta(tgt, -1, 1))
 
     def _moe_device(self, lw, T: int):
         """Decode-path MoE entirely on the device (graph-capturable): fused-norm router mat-vec -> dlp_moe_route ->
@@ -696,9 +740,7 @@ class LlamaEngine:
             self.next_tok[:B].copy_(torch.as_tensor(tokens, dtype=torch.int32), non_blocking=True)
         if hidden_in is not None:
             self.h[:B].copy_(hidden_in)
-        moe_host = self.cfg.is_moe and not (B <= 4 and self.comm.tp_size == 1 and self.cfg.n_expert <= 32 and
-                                            self.cfg.moe_norm_topk and not self.cfg.n_ff_shared and
-                                            next(iter(self.w.layers.values())).e_gate_s is not None)
+        moe_host = self.cfg.is_moe and not self._moe_grouped_ok(next(iter(self.w.layers.values())))   # routing through the host: no graph
         graphable = (use_graph and self.eval_callback is None and self.device.type == "cuda" and not moe_host
                      and not getattr(self.comm, "no_graph", False)
                      and not (self.sp_ok and B > 4))   # SP path passes host-side epochs as kernel arguments

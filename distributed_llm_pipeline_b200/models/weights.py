@@ -44,6 +44,7 @@ class LayerWeights:
     e_up_s: DeviceWeight | None = None
     e_down_s: DeviceWeight | None = None
     router_w: DeviceWeight | None = None
+    router_wp: DeviceWeight | None = None              # router_w zero-padded to a multiple of 128 rows
 
 
 @dataclass
@@ -234,6 +235,10 @@ def load_weights(src: str | GGUFModelFiles, device, layer_range: range | None = 
                 lw.e_up_s, lw.e_up = restack(lw.e_up)
                 lw.e_down_s, lw.e_down = restack(lw.e_down)
                 lw.router_w = DeviceWeight(GGMLType.F16, cfg.n_expert, cfg.n_embd, [lw.router.to(torch.float16).contiguous()])
+                # the same router padded to one full 128-row GEMM tile (token counts above the mat-vec range use the tcgen05 GEMM)
+                rp = torch.zeros(max(128, (cfg.n_expert + 127) // 128 * 128), cfg.n_embd, dtype=torch.float16, device=lw.router.device)
+                rp[:cfg.n_expert] = lw.router.to(torch.float16)
+                lw.router_wp = DeviceWeight(GGMLType.F16, rp.shape[0], cfg.n_embd, [rp])
             if cfg.n_ff_shared:   # qwen2moe shared expert (split across TP ranks like a dense FFN) + its gate vector
                 s0, s1 = _split(cfg.n_ff_shared, tp_size, tp_rank, 256 if tp_size > 1 else 1)
                 lw.w_gate = mat(p + "ffn_gate_shexp.weight", rows=(s0, s1))

@@ -422,6 +422,74 @@ def moe_route(logits: torch.Tensor, top_k: int, ids: torch.Tensor | None = None,
     return ids, weights
 
 
+class MoePlan:
+    """Device buffers of one routing plan (dlp_moe_plan_bufs) for up to `max_assign` (token, expert) assignments."""
+
+    def __init__(self, max_assign: int, n_expert: int, device, token_tile_min: int = 16):
+        i32 = torch.int32
+        cap = max_assign // token_tile_min + n_expert + 1
+        self.pos = torch.zeros(max_assign, dtype=i32, device=device)
+        self.src = torch.zeros(max_assign, dtype=i32, device=device)
+        self.bounds = torch.zeros(n_expert + 1, dtype=i32, device=device)
+        self.tile_expert = torch.zeros(cap, dtype=i32, device=device)
+        self.tile_row0 = torch.zeros(cap, dtype=i32, device=device)
+        self.tile_rows = torch.zeros(cap, dtype=i32, device=device)
+        self.n_tiles = torch.zeros(1, dtype=i32, device=device)
+
+        class _B(C.Structure):
+            _fields_ = [(n, C.c_void_p) for n in ("pos", "src", "bounds", "tile_expert", "tile_row0", "tile_rows", "n_tiles")]
+        self.c = _B(self.pos.data_ptr(), self.src.data_ptr(), self.bounds.data_ptr(), self.tile_expert.data_ptr(),
+                    self.tile_row0.data_ptr(), self.tile_rows.data_ptr(), self.n_tiles.data_ptr())
+
+
+def moe_route_ex(logits: torch.Tensor, n_expert: int, top_k: int, renorm: bool, ids: torch.Tensor, weights: torch.Tensor):
+    """softmax over the first n_expert columns -> top-k -> optional renormalisation (<= 256 experts), device only."""
+    lib = _lib.load()
+    lib.dlp_moe_route_ex.restype = C.c_int
+    lib.dlp_moe_route_ex.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]
+    _lib.check(lib.dlp_moe_route_ex(logits.data_ptr(), logits.stride(0), logits.shape[0], n_expert, top_k, int(renorm), ids.data_ptr(),
+                                    weights.data_ptr(), _stream()), "moe_route_ex")
+    _count()
+
+
+def moe_plan(ids: torch.Tensor, n_expert: int, token_tile: int, plan: MoePlan):
+    lib = _lib.load()
+    lib.dlp_moe_plan.restype = C.c_int
+    lib.dlp_moe_plan.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p]
+    _lib.check(lib.dlp_moe_plan(ids.data_ptr(), ids.numel(), n_expert, token_tile, C.byref(plan.c), _stream()), "moe_plan")
+    _count()
+
+
+def moe_gather(x: torch.Tensor, plan: MoePlan, top_k: int, n_assign: int, out: torch.Tensor):
+    lib = _lib.load()
+    lib.dlp_moe_gather.restype = C.c_int
+    lib.dlp_moe_gather.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p]
+    _lib.check(lib.dlp_moe_gather(x.data_ptr(), x.stride(0), plan.src.data_ptr(), top_k, n_assign, x.shape[1], out.data_ptr(), _stream()), "moe_gather")
+    _count()
+
+
+def linear_grouped(w: DeviceWeight, xs: torch.Tensor, out: torch.Tensor, out_mode: str, n_expert: int, rows_per_expert: int, token_tile: int,
+                   plan: MoePlan, w_up: DeviceWeight | None = None):
+    """Grouped tcgen05 GEMM over expert-sorted rows: out[row] (op)= xs[row] . W_expert(row)^T, one launch for all experts."""
+    lib = _lib.load()
+    lib.dlp_linear_grouped.restype = C.c_int
+    lib.dlp_linear_grouped.argtypes = [C.POINTER(_lib.dlp_weight), C.POINTER(_lib.dlp_weight), C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int,
+                                       C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p]
+    _lib.check(lib.dlp_linear_grouped(w.ref(), w_up.ref() if w_up is not None else None, xs.data_ptr(), out.data_ptr(), out.stride(0),
+                                      _OUT[out_mode], xs.shape[0], n_expert, rows_per_expert, token_tile, C.byref(plan.c), _stream()),
+               "linear_grouped")
+    _count()
+    return out
+
+
+def moe_combine(y: torch.Tensor, plan: MoePlan, weights: torch.Tensor, T: int, top_k: int, h: torch.Tensor):
+    lib = _lib.load()
+    lib.dlp_moe_combine.restype = C.c_int
+    lib.dlp_moe_combine.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p]
+    _lib.check(lib.dlp_moe_combine(y.data_ptr(), plan.pos.data_ptr(), weights.data_ptr(), T, top_k, y.shape[1], h.data_ptr(), _stream()), "moe_combine")
+    _count()
+
+
 def gemv_moe(w: DeviceWeight, x: torch.Tensor, out: torch.Tensor, out_mode: str, expert_id: torch.Tensor, rows_per_expert: int,
              w_up: DeviceWeight | None = None, norm_w: torch.Tensor | None = None, eps: float = 0.0,
              out_scale: torch.Tensor | None = None) -> torch.Tensor:

@@ -193,6 +193,34 @@ int dlp_moe_route(const float* logits, int T, int n_expert, int top_k, int32_t* 
 int dlp_gemv_moe(const dlp_weight* w0, const dlp_weight* w1, const void* x, const float* norm_w, float eps, void* y, int ldy,
                  int out_mode, const int32_t* expert_id_dev, int rows_per_expert, const float* out_scale_dev, void* stream);
 
+/* ---- mixture of experts, any token count: device-built routing plan + grouped tcgen05 GEMM (one launch per projection) ----
+ * dlp_moe_route_ex: like dlp_moe_route for up to 256 experts and rows of `ld` floats; renorm = 0 keeps the raw softmax weights (qwen2moe).
+ * dlp_moe_plan: from ids[n_assign] (n_assign = T * top_k, token-major) builds the expert-sorted order - pos[i] = sorted row of
+ *   assignment i, src[row] = assignment at a sorted row, bounds[n_expert + 1] - and the token-tile table of the grouped GEMMs
+ *   (expert, first sorted row, rows; *n_tiles entries; capacity n_assign / token_tile + n_expert).  Stable in token order.
+ * dlp_moe_gather: xs[row] = x[src[row] / top_k] (fp16 rows of K elements): the expert-sorted B operand.
+ * dlp_linear_grouped: y[row] (op)= xs[row] . W_e^T for every sorted row, e = the row's expert; w0 (w1 for SwiGLU) is the stack of
+ *   all experts [n_expert * rows_per_expert, K] in any supported weight type (block-quant decode fused as in dlp_linear).
+ *   Launches an upper bound of token tiles; the kernel reads the real count from the plan - nothing comes back to the host.
+ * dlp_moe_combine: h[t] += sum_j weights[t*k+j] * y[pos[t*k+j]] in slot order (deterministic).
+ * ref: mm_ids_helper + expert_bounds (ggml-cuda/mmid.cu), mul_mat_q ids_dst path (mmq.cuh:3459), topk_moe_cuda (topk-moe.cu),
+ * build_moe_ffn (llama.cpp/src/llama-graph.cpp:999-1266). */
+typedef struct dlp_moe_plan_bufs {
+    int32_t* pos;          /* [n_assign] */
+    int32_t* src;          /* [n_assign] */
+    int32_t* bounds;       /* [n_expert + 1] */
+    int32_t* tile_expert;  /* [n_assign / token_tile + n_expert] */
+    int32_t* tile_row0;
+    int32_t* tile_rows;
+    int32_t* n_tiles;      /* [1] */
+} dlp_moe_plan_bufs;
+int dlp_moe_route_ex(const float* logits, int ld, int T, int n_expert, int top_k, int renorm, int32_t* ids, float* weights, void* stream);
+int dlp_moe_plan(const int32_t* ids, int n_assign, int n_expert, int token_tile, dlp_moe_plan_bufs* bufs, void* stream);
+int dlp_moe_gather(const void* x, int ldx, const int32_t* src, int top_k, int n_assign, int K, void* xs, void* stream);
+int dlp_linear_grouped(const dlp_weight* w0, const dlp_weight* w1, const void* xs, void* y, int ldy, int out_mode, int n_assign, int n_expert,
+                       int rows_per_expert, int token_tile, const dlp_moe_plan_bufs* bufs, void* stream);
+int dlp_moe_combine(const float* y, const int32_t* pos, const float* weights, int T, int top_k, int E, float* h, void* stream);
+
 /* ---- tensor-parallel decode with the all-reduce fused into the mat-vecs (NVLink stores from inside the kernels, no NCCL) ----
  * Each rank owns, per all-reduce site, a symmetric buffer [2 parities][tp][DLP_AR_MAX_T][E] fp32 that every rank can store into:
  * through peer mappings (dlp_symm_alloc + dlp_ipc_export / dlp_ipc_import, or any symmetric-memory allocator) and, when the

@@ -25,10 +25,7 @@ def test_engine_gpu_matches_oracle(tmp_models, key):
     for i, t in enumerate(toks[:-1]):                 # mat-vec path, CUDA graph after the first call
         lg = eng.decode([sid], [t], sample=False)[0]
         assert nmse(ref_logits[i + 1], lg) < 1e-3, i
-    if not eng.cfg.is_moe:
-        assert any(k[:2] == (1, False) for k in eng._graphs)
-    elif eng.cfg.n_ff_shared:
-        assert not eng._graphs                      # shared-expert MoE decodes through the host-routed path (no graph)
+    assert any(k[:2] == (1, False) for k in eng._graphs)   # every family decodes inside a CUDA graph (MoE routing stays on the device)
 
 
 def test_graph_decode_feeds_back_device_tokens(tmp_models):
@@ -157,3 +154,23 @@ def test_engine_onepass_attention_matches_oracle(tmp_models, key):
         lg = eng.decode([sid], [t], sample=False)[0]
         assert nmse(ref_logits[i + 1], lg) < 1e-3, i
     assert any(k[:3] == (1, False, True) for k in eng._graphs) and any(k[:3] == (1, False, False) for k in eng._graphs)
+
+
+@pytest.mark.parametrize("key", [("tiny-moe", "F16"), ("tiny-qwen2moe", "F16"), ("tiny-qwen3moe", "F16")])
+@pytest.mark.parametrize("T", [1, 7, 64, 200])
+def test_moe_engine_any_token_count_on_device(tmp_models, key, T):
+    """Every MoE family, any token count: prefill through the grouped GEMM path and graph-captured decode, vs the fp32 oracle;
+    no launch of the step visits the host (the decode graph exists for all families, the shared-expert one included)."""
+    path = tmp_models[key]
+    ref = ReferenceModel.from_gguf(path)
+    g = torch.Generator().manual_seed(T)
+    prompt = torch.randint(3, ref.cfg.vocab_size, (T,), generator=g).tolist()
+    toks, ref_logits = ref.generate_greedy(prompt, 3)
+    eng = LlamaEngine(load_weights(path, "cuda"), n_ctx=256, max_seqs=2, page_size=16, max_batch_tokens=256)
+    sid = eng.alloc_seq()
+    lg = eng.prefill(sid, prompt)
+    assert nmse(ref_logits[0], lg) < 1e-3
+    for i, t in enumerate(toks[:-1]):
+        lg = eng.decode([sid], [t], sample=False)[0]
+        assert nmse(ref_logits[i + 1], lg) < 1e-3, i
+    assert any(k[:2] == (1, False) for k in eng._graphs)

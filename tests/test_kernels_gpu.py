@@ -531,3 +531,67 @@ def test_moe_route_and_expert_indexed_gemv(t):
     for j in range(k):
         ops.gemv_moe(Wd, act[j:j + 1], hout, "add", ids[j:j + 1], E, out_scale=w[j:j + 1])
     assert nmse(href, hout) < (1e-4 if t.name.startswith("Q") else 1e-6)
+
+
+@pytest.mark.parametrize("t", [GGMLType.F16, GGMLType.Q8_0, GGMLType.Q4_K])
+@pytest.mark.parametrize("T,nE,k", [(1, 4, 2), (7, 8, 2), (64, 8, 2), (300, 8, 2), (33, 60, 4), (129, 128, 8)])
+def test_moe_grouped_gemm_pipeline(t, T, nE, k):
+    """route -> plan -> gather -> grouped SwiGLU GEMM -> grouped down GEMM -> combine, against per-token fp32 math with the
+    same (dequantised) expert weights.  Covers experts that receive no token, partial token tiles and > 32 experts."""
+    from distributed_llm_pipeline_b200.gguf.quants import dequantize, quantize
+    import numpy as np
+    E, F = 256, 256
+    g = torch.Generator().manual_seed(100 + T + nE)
+    logits = torch.randn(T, nE, generator=g).to(DEV)
+    if T >= 64:
+        logits[:, 1] = -30.0                                   # expert 1 never selected: an empty group in the plan
+    A = T * k
+    ids = torch.zeros(A, dtype=torch.int32, device=DEV)
+    w = torch.zeros(A, dtype=torch.float32, device=DEV)
+    for renorm in (True, False):
+        ops.moe_route_ex(logits, nE, k, renorm, ids, w)
+        pr = torch.softmax(logits, -1)
+        tw, ti = pr.topk(k, -1)
+        assert torch.equal(ids.view(T, k).long(), ti)
+        assert torch.allclose(w.view(T, k), tw / tw.sum(-1, keepdim=True) if renorm else tw, atol=1e-6)
+    bt = 16 if A // nE <= 16 else 32 if A // nE <= 32 else 64
+    plan = ops.MoePlan(A, nE, DEV)
+    ops.moe_plan(ids, nE, bt, plan)
+    pos, src, bounds = plan.pos.long(), plan.src.long(), plan.bounds.tolist()
+    assert bounds[0] == 0 and bounds[-1] == A
+    assert torch.equal(src[pos], torch.arange(A, device=DEV))                     # a permutation ...
+    for e in range(nE):
+        rows = src[bounds[e]:bounds[e + 1]]
+        assert bool((ids[rows] == e).all()) and bool((rows[1:] > rows[:-1]).all())   # ... grouped by expert, stable in token order
+    nt = int(plan.n_tiles)
+    assert nt == sum((bounds[e + 1] - bounds[e] + bt - 1) // bt for e in range(nE))
+    assert int(plan.tile_rows[:nt].sum()) == A
+    gate = torch.randn(nE * F, E, generator=g) * 0.05
+    up = torch.randn(nE * F, E, generator=g) * 0.05
+    down = torch.randn(nE * E, F, generator=g) * 0.05
+    Wg, Wu, Wd = (DeviceWeight.from_dense(m, t, DEV) for m in (gate, up, down))
+    deq = lambda m: torch.from_numpy(dequantize(quantize(m.numpy(), t), t, tuple(m.shape)).astype(np.float32)).to(DEV)
+    dg, du, dd = deq(gate), deq(up), deq(down)
+    x = torch.randn(T, E, generator=g).half().to(DEV)
+    xs = torch.zeros(A, E, dtype=torch.float16, device=DEV)
+    ops.moe_gather(x, plan, k, A, xs)
+    assert torch.equal(xs, x[src // k])
+    act = torch.zeros(A, F, dtype=torch.float16, device=DEV)
+    ops.linear_grouped(Wg, xs, act, "swiglu", nE, F, bt, plan, w_up=Wu)
+    y = torch.zeros(A, E, dtype=torch.float32, device=DEV)
+    ops.linear_grouped(Wd, act, y, "f32", nE, E, bt, plan)
+    h = torch.randn(T, E, generator=g).to(DEV)
+    h_ref = h.clone()
+    ops.moe_combine(y, plan, w, T, k, h)
+    tol = 3e-4 if t.name.startswith("Q") else 2e-5
+    for e in range(nE):
+        sel = (ids == e).nonzero().flatten()
+        if sel.numel() == 0:
+            continue
+        xe = x[sel // k].float()
+        a_ref = torch.nn.functional.silu(xe @ dg[e * F:(e + 1) * F].T) * (xe @ du[e * F:(e + 1) * F].T)
+        assert nmse(a_ref, act[pos[sel]]) < tol, e
+        y_ref = act[pos[sel]].float() @ dd[e * E:(e + 1) * E].T
+        assert nmse(y_ref, y[pos[sel]]) < tol, e
+        h_ref.index_add_(0, sel // k, w[sel][:, None] * y[pos[sel]])
+    assert nmse(h_ref, h) < 1e-6

@@ -144,3 +144,27 @@ def test_native_supervisor_restarts_engine_service(front):
     events = [json.loads(b[6:]) for b in text.split("\n\n") if b.startswith("data: ")]
     assert any(e["msg_type"] == "token" for e in events)
     assert any("restart" in e["content"] for e in events if e["msg_type"] == "log")
+
+
+def test_native_front_over_tensor_parallel_backend(tmp_models):
+    """dlp-orchestrator --spawn "<engine service> --tp 2": the C++ front-end supervises a service that is itself a grid of
+    processes (it re-starts under torchrun; rank 0 serves, rank 1 replays).  The reference's equivalent is the hard-coded
+    `llama-cli --rpc a,b` child of `orchestrator/src/main.rs:35-57`."""
+    native.build()
+    fport, bport = _free_port(), _free_port()
+    spawn = (f"{sys.executable} -m distributed_llm_pipeline_b200.serving.backend -m {tmp_models[('tiny', 'F16')]} "
+             f"--device cpu --port {bport} -c 128 -np 2 -b 32 --tp 2")
+    env = dict(os.environ, PYTHONPATH=REPO, CUDA_VISIBLE_DEVICES="", DLP_MASTER_PORT=str(_free_port()))
+    p = subprocess.Popen([native.path("dlp-orchestrator"), "--host", "127.0.0.1", "--port", str(fport), "--backend", f"127.0.0.1:{bport}",
+                          "--static", os.path.join(REPO, "distributed_llm_pipeline_b200", "serving", "static"), "--spawn", spawn, "-n", "8"],
+                         env=env, stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, preexec_fn=os.setsid)
+    try:
+        p.stdout.readline()
+        head, payload = _post_chat(fport, json.dumps({"prompt": "a b c"}).encode())
+        assert head.startswith("HTTP/1.1 200")
+        events = [json.loads(b[6:]) for b in _dechunk(payload).decode().split("\n\n") if b.startswith("data: ")]
+        logs = "".join(e["content"] for e in events if e["msg_type"] == "log")
+        assert "grid: 1 pipeline stage(s) x 2 tensor-parallel rank(s)" in logs and logs.count("load_tensors: stage") == 2
+        assert sum(e["msg_type"] == "token" for e in events) >= 1
+    finally:
+        os.killpg(os.getpgid(p.pid), signal.SIGTERM)

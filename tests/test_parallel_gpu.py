@@ -1,6 +1,8 @@
 """Multi-GPU paths on real devices (skipped below 2 GPUs): TP over NCCL, TP with the all-reduce fused into the
 mat-vec kernels (NVLink peer stores), and a 2-stage pipeline - each against the fp32 oracle."""
 import os
+import sys as _sys
+_sys.path.insert(0, os.path.dirname(os.path.abspath(__file__)))
 import subprocess
 import sys
 
@@ -67,3 +69,29 @@ def test_pp2_tp2_fused_gpu(tmp_models):
     _need(4)
     r = _torchrun(4, ["--model", tmp_models[("tiny128", "F16")], "--device", "cuda", "--pp", "2", "--impl", "fused"], 29741)
     assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
+
+
+@pytest.mark.parametrize("flags", [("--tp", "2"), ("--tp", "2", "--tp-impl", "nccl"), ("--pp", "2")], ids=["tp2-fused", "tp2-nccl", "pp2"])
+def test_orchestrator_over_gpu_grid(tmp_models, flags):
+    """POST /completion to an orchestrator whose engine is a 2-GPU grid (fused TP, NCCL TP, 2-stage pipeline): same greedy text
+    as the single-GPU engine, per-rank "offloaded" lines in the /chat log stream."""
+    _need(2)
+    import json
+    from test_distributed_serving import PROMPT, _Proc, _chat_events, _completion, _free_port
+    from distributed_llm_pipeline_b200.serving.orchestrator import build_service
+    from distributed_llm_pipeline_b200.serving.sampler import SamplingParams
+    model = tmp_models[("tiny128", "F16")]
+    sched, _, _ = build_service(model, device="cuda", n_ctx=128, n_slots=2, n_batch=32)
+    want = sched.generate(PROMPT, n_predict=8, sampling=SamplingParams(temperature=0.0), ignore_eos=True).text
+    port = _free_port()
+    srv = _Proc(["-m", "distributed_llm_pipeline_b200.serving.orchestrator", "-m", model, "--device", "cuda", "--port", str(port),
+                 "-c", "128", "-np", "2", "-b", "32", "-n", "8", *flags], port)
+    try:
+        srv.wait_ready(240)
+        d = _completion(port, 8)
+        assert d["content"] == want, (d["content"], want)
+        logs = "".join(e["content"] for e in _chat_events(port, PROMPT) if e["msg_type"] == "log")
+        assert logs.count("load_tensors: stage") == 2 and "grid:" in logs
+        json.dumps(d)
+    finally:
+        srv.stop()
