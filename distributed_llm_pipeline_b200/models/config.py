@@ -86,6 +86,8 @@ PRESETS: dict[str, ModelConfig] = {
     # enough heads / width for every tensor-parallel degree up to 8 (per-rank K of the row-parallel mat-vecs stays a multiple of 256)
     "tiny-tp8": ModelConfig(name="tiny-tp8", vocab_size=2048, n_embd=2048, n_layer=2, n_head=16, n_head_kv=8,
                             head_dim=128, n_ff=2048, n_ctx_train=1024, rope_theta=10000.0, rope_dim=128),
+    "tiny-moe-tp": ModelConfig(name="tiny-moe-tp", vocab_size=512, n_embd=512, n_layer=2, n_head=8, n_head_kv=4, head_dim=64, n_ff=512,
+                               n_ctx_train=512, rope_theta=10000.0, rope_dim=64, n_expert=4, n_expert_used=2),
     "tiny-moe": ModelConfig(name="tiny-moe", vocab_size=512, n_embd=256, n_layer=2, n_head=4, n_head_kv=2,
                             head_dim=64, n_ff=256, n_ctx_train=512, rope_theta=10000.0, rope_dim=64, n_expert=4,
                             n_expert_used=2),

@@ -59,6 +59,18 @@ def test_tp_wide_fused_gpu(tmp_models, n):
     assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
 
 
+@pytest.mark.parametrize("ftype", ["F16", "Q8_0"])
+@pytest.mark.parametrize("batch", [1, 3])
+def test_tp2_moe_gpu(tmp_models, ftype, batch):
+    """Mixture of experts under tensor parallelism: every expert's n_ff is sharded, routing + grouped GEMM stay on the device,
+    the combine's partial sums are all-reduced (the reference cannot split expert weights at all: MUL_MAT_ID asserts,
+    ggml-cuda.cu:2274)."""
+    _need(2)
+    r = _torchrun(2, ["--model", tmp_models[("tiny-moe-tp", ftype)], "--device", "cuda", "--impl", "fused", "--batch", str(batch), "--greedy", "8"],
+                  29751 + batch)
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
+
+
 def test_pp2_gpu(tmp_models):
     _need(2)
     r = _torchrun(2, ["--model", tmp_models[("tiny128", "F16")], "--device", "cuda", "--pp", "2", "--batch", "2"], 29731)

@@ -73,3 +73,40 @@ def test_fit_params_and_list_devices(tmp_models):
     assert any(d.startswith("CPU") for d in list_devices())
     out = _run("dlp_cli.py", "--list-devices")
     assert "Available devices" in out
+
+
+def test_serve_bench_against_orchestrator(tmp_models):
+    """The load generator (scripts/server-bench.py counterpart) drives /completion (token-array prompts, streaming) and /chat."""
+    import asyncio
+    import json
+    import socket
+    import subprocess
+    import sys
+    import threading
+    import time
+    from distributed_llm_pipeline_b200.serving.orchestrator import Orchestrator, build_service
+    sched, info, logs = build_service(tmp_models[("tiny", "F16")], device="cpu", n_ctx=128, n_slots=4, n_batch=32)
+    sched.start()
+    orch = Orchestrator(sched, info, n_predict=6, startup_logs=logs)
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    port = s.getsockname()[1]
+    s.close()
+    loop = asyncio.new_event_loop()
+    threading.Thread(target=lambda: loop.run_until_complete(orch.serve("127.0.0.1", port)), daemon=True).start()
+    for _ in range(100):
+        try:
+            socket.create_connection(("127.0.0.1", port), timeout=0.2).close()
+            break
+        except OSError:
+            time.sleep(0.05)
+    try:
+        for route in ("/completion", "/chat"):
+            r = subprocess.run([sys.executable, os.path.join(REPO, "tools", "serve_bench.py"), "--port", str(port), "--route", route, "-c", "1,3",
+                                "--prompt-tokens", "12", "-n", "6", "--vocab", "500"], capture_output=True, text=True, timeout=120)
+            assert r.returncode == 0, r.stderr
+            rows = [json.loads(l) for l in r.stdout.splitlines() if l.startswith("{")]
+            assert [x["concurrency"] for x in rows] == [1, 3]
+            assert all(x["ok"] == x["concurrency"] and x["agg_tok_s"] > 0 and x["ttft_ms_p50"] > 0 for x in rows), rows
+    finally:
+        sched.stop()

@@ -21,7 +21,8 @@ BENCH = [
     Opt(("-n", "--n-gen"), "comma separated generation sizes", "128", str),
     Opt(("-r", "--repetitions"), "repetitions per test", 3, int),
     Opt(("-o", "--output"), "md | json | jsonl | csv | sql", "md", str, choices=("md", "json", "jsonl", "csv", "sql")),
-    Opt(("--batch",), "decode batch size (sequences decoded together)", 1, int),
+    Opt(("--batch",), "comma separated decode batch sizes (sequences decoded together)", "1", str),
+    Opt(("--microbatches",), "pipeline micro-batches per decode round (0 = one per stage when the batch allows)", 0, int),
 ]
 
 
@@ -53,7 +54,8 @@ def main(argv=None):
     pps = [int(x) for x in a.n_prompt.split(",") if int(x) > 0]
     gens = [int(x) for x in a.n_gen.split(",") if int(x) > 0]
     n_ctx = max(pps + [0]) + max(gens + [0]) + 8
-    eng = LlamaEngine(w, n_ctx=max(n_ctx, a.ctx_size), max_seqs=max(1, a.batch), page_size=64, max_batch_tokens=max(a.ubatch_size, 16),
+    batches = [max(1, int(x)) for x in str(a.batch).split(",")]
+    eng = LlamaEngine(w, n_ctx=max(n_ctx, a.ctx_size), max_seqs=max(batches), page_size=64, max_batch_tokens=max(a.ubatch_size, max(batches), 16),
                       comm=comm, first_stage=grid.first_stage, last_stage=grid.last_stage)
     stage = None
     if grid.pp > 1:
@@ -92,27 +94,33 @@ def main(argv=None):
                 ts.append(n_p / ms * 1e3)
         rows.append({"test": f"pp{n_p}", "n_prompt": n_p, "n_gen": 0, "avg_ts": statistics.mean(ts), "stddev_ts": statistics.pstdev(ts)})
     for n_g in gens:
+      for B in batches:
+        # pipeline stages overlap only across micro-batches: a batch is cut into one sequence group per stage (north star:
+        # "send/recv overlapped with the next micro-batch's compute"); a single sequence runs the stages serially
+        n_mb = min(B, a.microbatches or grid.pp) if stage else 1
         ts = []
         for rep in range(a.repetitions + 1):
-            sids = fresh(a.batch)
+            sids = fresh(B)
             for s in sids:
                 (stage.prefill(s, [1]) if stage else eng.prefill(s, [1]))
-            first = torch.randint(3, cfg.vocab_size, (a.batch,), generator=g, dtype=torch.int32)
+            first = torch.randint(3, cfg.vocab_size, (B,), generator=g, dtype=torch.int32)
+            cut = [B * i // n_mb for i in range(n_mb + 1)]
+            groups = [sids[cut[i]:cut[i + 1]] for i in range(n_mb)]
 
             def run():
                 if stage:
-                    stage.decode_round([sids], [first], feedback=n_g > 1)
+                    stage.decode_round(groups, [first[cut[i]:cut[i + 1]] for i in range(n_mb)], feedback=n_g > 1)
                     for i in range(n_g - 1):
-                        stage.decode_round([sids], None, feedback=i < n_g - 2)
+                        stage.decode_round(groups, None, feedback=i < n_g - 2)
                 else:
                     eng.decode(sids, first)
                     for _ in range(n_g - 1):
                         eng.decode(sids)
             ms = timed(run)
             if rep:
-                ts.append(n_g * a.batch / ms * 1e3)
-        rows.append({"test": f"tg{n_g}" + (f"@b{a.batch}" if a.batch > 1 else ""), "n_prompt": 0, "n_gen": n_g, "avg_ts": statistics.mean(ts),
-                     "stddev_ts": statistics.pstdev(ts)})
+                ts.append(n_g * B / ms * 1e3)
+        rows.append({"test": f"tg{n_g}" + (f"@b{B}" if B > 1 else ""), "n_prompt": 0, "n_gen": n_g, "batch": B, "microbatches": n_mb,
+                     "avg_ts": statistics.mean(ts), "stddev_ts": statistics.pstdev(ts)})
     if grid.rank == 0:
         meta = {"model": os.path.basename(a.model), "params": cfg.n_params(), "size_bytes": w.nbytes(), "pp": grid.pp, "tp": grid.tp,
                 "tp_impl": a.tp_impl if grid.tp > 1 else None, "backend": "dlp_b200"}
