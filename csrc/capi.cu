@@ -159,18 +159,21 @@ int dlp_gemm_sp(const dlp_weight* w0, const dlp_weight* w1, const void* x, int l
     if (coll) {
         c.x_flags = coll->x_flags; c.x_rows_per_src = coll->x_rows_per_src; c.x_epoch = coll->x_epoch; c.error = coll->error;
         for (int i = 0; i < 8; ++i) { c.rs_peer_buf[i] = coll->rs_peer_buf[i]; c.rs_peer_flags[i] = coll->rs_peer_flags[i]; }
-        c.rs_done = coll->rs_done; c.rs_rows = coll->rs_rows; c.rs_rank = coll->rs_rank; c.rs_tp = coll->rs_tp; c.rs_epoch = coll->rs_epoch;
+        c.rs_done = coll->rs_done; c.rs_rows = coll->rs_rows; c.rs_rank = coll->rs_rank; c.rs_tp = coll->rs_tp; c.rs_epoch = coll->rs_epoch; c.step = coll->step;
         DLP_REQUIRE(c.x_flags == nullptr || c.x_rows_per_src > 0, "dlp_gemm_sp: x_rows_per_src must be positive");
     }
     const int wt = w0->wtype;
     cudaStream_t s = (cudaStream_t)stream;
+    void* ws = coll ? coll->ws : nullptr;
+    const size_t ws_bytes = coll ? coll->ws_bytes : 0;
+    const int sk = ws ? 0 : 1;     // with a workspace: automatic deterministic split-K for skinny shards
     if (wt == DLP_W_F16 || wt == DLP_W_BF16)
-        return gemm_f16(w0->base, w1 ? w1->base : nullptr, w0->K, x, ldx, y, ldy, T, w0->N, w0->K, epilogue, wt == DLP_W_BF16, 1, s,
-                        coll ? &c : nullptr);
+        return gemm_f16(w0->base, w1 ? w1->base : nullptr, w0->K, x, ldx, y, ldy, T, w0->N, w0->K, epilogue, wt == DLP_W_BF16, sk, s,
+                        coll ? &c : nullptr, nullptr, ws, ws_bytes);
     const QWeight q0 = to_qw(w0);
     QWeight q1;
     if (w1) q1 = to_qw(w1);
-    return gemm_quant(q0, w1 ? &q1 : nullptr, wt, x, ldx, y, ldy, T, epilogue, 1, s, coll ? &c : nullptr);
+    return gemm_quant(q0, w1 ? &q1 : nullptr, wt, x, ldx, y, ldy, T, epilogue, sk, s, coll ? &c : nullptr, nullptr, ws, ws_bytes);
 }
 
 int dlp_rs_norm_ag(const dlp_rs_norm_ag_desc* d, void* stream) {
@@ -180,7 +183,7 @@ int dlp_rs_norm_ag(const dlp_rs_norm_ag_desc* d, void* stream) {
     a.h_shard = d->h_shard; a.red_buf = d->red_buf; a.red_flags = d->red_flags; a.red_epoch = d->red_epoch;
     a.norm_w = d->norm_w; a.eps = d->eps;
     for (int i = 0; i < 8; ++i) { a.ag_peer_buf[i] = (__half*)d->ag_peer_buf[i]; a.ag_peer_flags[i] = d->ag_peer_flags[i]; }
-    a.ag_epoch = d->ag_epoch; a.done = d->done; a.error = d->error; a.rank = d->rank; a.tp = d->tp; a.rows = d->rows; a.E = d->E;
+    a.ag_epoch = d->ag_epoch; a.done = d->done; a.error = d->error; a.rank = d->rank; a.tp = d->tp; a.rows = d->rows; a.E = d->E; a.step = d->step;
     return rs_norm_ag(a, (cudaStream_t)stream);
 }
 
@@ -198,18 +201,22 @@ int dlp_linear(const dlp_weight* w0, const dlp_weight* w1, const void* x, const 
     const int epi = out_mode == DLP_OUT_F16 ? 0 : out_mode == DLP_OUT_F32 ? 1 : out_mode == DLP_OUT_ADD_F32 ? 2 : 3;
     const int wt = w0->wtype;
     cudaStream_t s = (cudaStream_t)stream;
-    if (wt == DLP_W_F16 || wt == DLP_W_BF16)
-        return gemm_f16(w0->base, w1 ? w1->base : nullptr, w0->K, x, w0->K, y, ldy, T, w0->N, w0->K, epi,
-                        wt == DLP_W_BF16, 0, s);
-    // block-quantised: the decode is fused into the GEMM's A-operand producer (no scratch).  DLP_GEMM_DEQUANT_SCRATCH=1
-    // selects the older two-pass path (decode to fp16 scratch, then the dense GEMM) for A/B runs.
     static int two_pass = -1;
     if (two_pass < 0) { const char* e = getenv("DLP_GEMM_DEQUANT_SCRATCH"); two_pass = (e && e[0] == '1') ? 1 : 0; }
+    // (unless the two-pass dequant path owns it, `scratch` is the split-K workspace: 16 KB of zero-initialised tile counters
+    //  followed by room for the partial tiles; NULL = no split-K for the store epilogues)
+    void* ws = two_pass ? nullptr : scratch;
+    const size_t ws_bytes = two_pass ? 0 : scratch_bytes;
+    if (wt == DLP_W_F16 || wt == DLP_W_BF16)
+        return gemm_f16(w0->base, w1 ? w1->base : nullptr, w0->K, x, w0->K, y, ldy, T, w0->N, w0->K, epi,
+                        wt == DLP_W_BF16, 0, s, nullptr, nullptr, ws, ws_bytes);
+    // block-quantised: the decode is fused into the GEMM's A-operand producer (no scratch).  DLP_GEMM_DEQUANT_SCRATCH=1
+    // selects the older two-pass path (decode to fp16 scratch, then the dense GEMM) for A/B runs.
     if (!two_pass) {
         const QWeight q0 = to_qw(w0);
         QWeight q1;
         if (w1) q1 = to_qw(w1);
-        return gemm_quant(q0, w1 ? &q1 : nullptr, wt, x, w0->K, y, ldy, T, epi, 0, s);
+        return gemm_quant(q0, w1 ? &q1 : nullptr, wt, x, w0->K, y, ldy, T, epi, 0, s, nullptr, nullptr, ws, ws_bytes);
     }
     const size_t per = (size_t)w0->N * w0->K * 2;
     const size_t need = per * (w1 ? 2 : 1);
@@ -243,7 +250,7 @@ int dlp_moe_combine(const float* y, const int32_t* pos, const float* weights, in
     return moe_combine(y, pos, weights, T, top_k, E, h, (cudaStream_t)stream);
 }
 int dlp_linear_grouped(const dlp_weight* w0, const dlp_weight* w1, const void* xs, void* y, int ldy, int out_mode, int n_assign, int n_expert,
-                       int rows_per_expert, int token_tile, const dlp_moe_plan_bufs* b, void* stream) {
+                       int rows_per_expert, int token_tile, const dlp_moe_plan_bufs* b, void* ws, size_t ws_bytes, void* stream) {
     DLP_REQUIRE(w0 && w0->base && xs && y && b && b->tile_expert && n_assign > 0 && n_expert > 0, "dlp_linear_grouped: bad argument");
     DLP_REQUIRE(out_mode == DLP_OUT_F16 || out_mode == DLP_OUT_F32 || out_mode == DLP_OUT_SWIGLU_F16, "dlp_linear_grouped: output mode %d", out_mode);
     DLP_REQUIRE(w0->N == n_expert * rows_per_expert, "dlp_linear_grouped: weight has %d rows, expected %d x %d", w0->N, n_expert, rows_per_expert);
@@ -255,12 +262,12 @@ int dlp_linear_grouped(const dlp_weight* w0, const dlp_weight* w1, const void* x
     const int wt = w0->wtype;
     cudaStream_t s = (cudaStream_t)stream;
     if (wt == DLP_W_F16 || wt == DLP_W_BF16)
-        return gemm_f16(w0->base, w1 ? w1->base : nullptr, w0->K, xs, w0->K, y, ldy, n_assign, rows_per_expert, w0->K, epi, wt == DLP_W_BF16, 1, s,
-                        nullptr, &g);
+        return gemm_f16(w0->base, w1 ? w1->base : nullptr, w0->K, xs, w0->K, y, ldy, n_assign, rows_per_expert, w0->K, epi, wt == DLP_W_BF16,
+                        ws ? 0 : 1, s, nullptr, &g, ws, ws_bytes);
     const QWeight q0 = to_qw(w0);
     QWeight q1;
     if (w1) q1 = to_qw(w1);
-    return gemm_quant(q0, w1 ? &q1 : nullptr, wt, xs, w0->K, y, ldy, n_assign, epi, 1, s, nullptr, &g);
+    return gemm_quant(q0, w1 ? &q1 : nullptr, wt, xs, w0->K, y, ldy, n_assign, epi, ws ? 0 : 1, s, nullptr, &g, ws, ws_bytes);
 }
 
 int dlp_dequant_rows_f32(const dlp_weight* w, const int32_t* row_ids, int n_rows, float* out, int ld_out, void* stream) {

@@ -83,7 +83,7 @@ __global__ void __launch_bounds__(1024) argmax_tp_kernel(const float* __restrict
         if (ov > best || (ov == best && oi < bi)) { best = ov; bi = oi; }
     }
     const int par = *x.epoch & 1;
-    const size_t slot = ((size_t)par * x.tp + x.rank) * AR_MAX_T + b;
+    const size_t slot = ((size_t)par * x.tp + x.rank) * TOKX_MAX_R + b;
     if (lane == 0) {   // larger word = better candidate: value first, then the lower global token id
         const unsigned long long w = ((unsigned long long)ord_f32(best) << 32) | (0xFFFFFFFFu - (uint32_t)(v0 + bi));
         if (x.mc_slots != nullptr) {
@@ -94,7 +94,7 @@ __global__ void __launch_bounds__(1024) argmax_tp_kernel(const float* __restrict
     }
     unsigned long long w = 0;
     if (lane < x.tp) {
-        const unsigned long long* p = x.slots + ((size_t)par * x.tp + lane) * AR_MAX_T + b;
+        const unsigned long long* p = x.slots + ((size_t)par * x.tp + lane) * TOKX_MAX_R + b;
         const long long t0 = clock64();
         while (true) {
             asm volatile("ld.volatile.global.u64 %0, [%1];" : "=l"(w) : "l"(p) : "memory");
@@ -102,7 +102,7 @@ __global__ void __launch_bounds__(1024) argmax_tp_kernel(const float* __restrict
             if (x.error && *reinterpret_cast<volatile int*>(x.error)) break;
             if (clock64() - t0 > (1ll << 34)) { if (x.error) atomicExch(x.error, 1); break; }
         }
-        x.slots[((size_t)(par ^ 1) * x.tp + lane) * AR_MAX_T + b] = 0;   // re-arm the other parity
+        x.slots[((size_t)(par ^ 1) * x.tp + lane) * TOKX_MAX_R + b] = 0;   // re-arm the other parity
     }
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) {
@@ -113,7 +113,7 @@ __global__ void __launch_bounds__(1024) argmax_tp_kernel(const float* __restrict
 }
 
 int argmax_tp(const float* logits, int R, int V, int ld, int v0, const TokX& x, int* out, cudaStream_t s) {
-    DLP_REQUIRE(R >= 1 && R <= AR_MAX_T && V > 0 && x.tp >= 1 && x.tp <= 8 && x.slots && x.epoch, "argmax_tp: bad argument");
+    DLP_REQUIRE(R >= 1 && R <= TOKX_MAX_R && V > 0 && x.tp >= 1 && x.tp <= 8 && x.slots && x.epoch, "argmax_tp: bad argument");
     DLP_CHECK_CUDA(launch_pdl(argmax_tp_kernel, dim3(R), dim3(1024), 0, s, logits, V, ld, v0, x, out));
     return 0;
 }
@@ -136,11 +136,12 @@ __global__ void __launch_bounds__(256) rs_norm_ag_kernel(const RsNormAg a) {
     if (a.red_buf != nullptr) {
         if ((int)threadIdx.x < a.tp && !(a.error && *reinterpret_cast<volatile int*>(a.error))) {
             const long long t0 = clock64();
+            const uint32_t red_epoch = sp_epoch(a.step, a.red_epoch);
             uint32_t v;
             do {
                 asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(a.red_flags + threadIdx.x) : "memory");
                 if (clock64() - t0 > (1ll << 34)) { if (a.error) atomicExch(a.error, 1); break; }
-            } while ((int32_t)(v - a.red_epoch) < 0);
+            } while ((int32_t)(v - red_epoch) < 0);
         }
         __syncthreads();
     }
@@ -179,7 +180,7 @@ __global__ void __launch_bounds__(256) rs_norm_ag_kernel(const RsNormAg a) {
             *a.done = 0;
             __threadfence_system();
             for (int pr = 0; pr < a.tp; ++pr)
-                asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(a.ag_peer_flags[pr] + a.rank), "r"(a.ag_epoch) : "memory");
+                asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(a.ag_peer_flags[pr] + a.rank), "r"(sp_epoch(a.step, a.ag_epoch)) : "memory");
         }
     }
 }

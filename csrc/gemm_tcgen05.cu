@@ -29,6 +29,10 @@ struct GemmParams {
     int k_blocks_per_split;
     GemmCollective coll;   // fused all-gather (X side) / reduce-scatter (Y side); zero-initialised = none
     GemmGroup grp;         // grouped (MoE) launch: per-tile expert / row range table built on the device
+    // split-K with a deterministic fix-up (any epilogue): every split stores its fp32 partial tile into `ws`, the split that
+    // arrives last at the tile's counter adds the partials in split order and runs the epilogue.  nullptr: not used.
+    float* ws;
+    unsigned* ws_counters;
 };
 
 template <int BT, int NA>
@@ -197,12 +201,13 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tm_w0, const __grid_cons
                 // ranks; wait for exactly those owners, then order the acquired generic-proxy view before the TMA reads
                 const int s0 = t0 / p.coll.x_rows_per_src, s1 = min(p.T - 1, t0 + BT - 1) / p.coll.x_rows_per_src;
                 const long long c0 = clock64();
+                const uint32_t x_epoch = sp_epoch(p.coll.step, p.coll.x_epoch);
                 for (int src = s0; src <= s1; ++src) {
                     uint32_t v;
                     do {
                         asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p.coll.x_flags + src) : "memory");
                         if (clock64() - c0 > (1ll << 34)) { if (p.coll.error) atomicExch(p.coll.error, 1); break; }
-                    } while ((int32_t)(v - p.coll.x_epoch) < 0);
+                    } while ((int32_t)(v - x_epoch) < 0);
                 }
                 fence_proxy_async_global();
             }
@@ -265,17 +270,18 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tm_w0, const __grid_cons
         }
         // ===== epilogue: 4 warps, warp%4 selects the TMEM lane quarter =====
         const int q = warp & 3;
-        const int n = n_out0 + q * 32 + lane;
+        const int n_local = q * 32 + lane;
+        const int n = n_out0 + n_local;
         if (num_kb > 0) {
             mbar_wait(tmem_full_bar, 0);
             tc_fence_after();
         }
         const uint32_t lane_addr = tmem_base + ((uint32_t)(q * 32) << 16);
         constexpr int CH = BT >= 32 ? 32 : 16;
-#pragma unroll 1
-        for (int c = 0; c < BT / CH; ++c) {
-            if (t0 + c * CH >= t_end) break;  // warp-uniform
-            uint32_t r0[CH], r1[CH];
+        const int S = gridDim.z;
+        const bool split_ws = p.ws != nullptr && S > 1;
+        const size_t tile = (size_t)blockIdx.y * gridDim.x + blockIdx.x;
+        auto load_acc = [&](int c, uint32_t (&r0)[CH], uint32_t (&r1)[CH]) {
             if (num_kb > 0) {
                 if constexpr (CH == 32) {
                     tmem_ld_32x32(lane_addr + c * CH, r0);
@@ -289,6 +295,8 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tm_w0, const __grid_cons
 #pragma unroll
                 for (int j = 0; j < CH; ++j) { r0[j] = 0; r1[j] = 0; }
             }
+        };
+        auto run_epilogue = [&](int c, const uint32_t (&r0)[CH], const uint32_t (&r1)[CH]) {
             if (n < p.N) {
                 // one specialised store loop per epilogue (dispatch hoisted out of the per-element loop: a switch with the
                 // reduce-scatter address arithmetic inside it cost 35-50 % of the whole GEMM, see profiles/r1_gemm_ab.txt)
@@ -301,6 +309,56 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tm_w0, const __grid_cons
                     case EPI_SWIGLU_F16: if (NA == 2) epi_loop<EPI_SWIGLU_F16, CH>(p, r0, r1, tb, n, t_end); break;
                     case EPI_RS_PUSH_F32: epi_loop<EPI_RS_PUSH_F32, CH>(p, r0, r1, tb, n, t_end); break;
                 }
+            }
+        };
+        if (!split_ws) {
+#pragma unroll 1
+            for (int c = 0; c < BT / CH; ++c) {
+                if (t0 + c * CH >= t_end) break;  // warp-uniform
+                uint32_t r0[CH], r1[CH];
+                load_acc(c, r0, r1);
+                run_epilogue(c, r0, r1);
+            }
+        } else {
+            // partial tile -> workspace [tile][split][accumulator][token][128 features] (128 consecutive floats per store round)
+            __shared__ int s_last;
+            float* wsp = p.ws + ((tile * S + blockIdx.z) * NA) * (size_t)BT * GEMM_BM;
+#pragma unroll 1
+            for (int c = 0; c < BT / CH; ++c) {
+                if (t0 + c * CH >= t_end) break;
+                uint32_t r0[CH], r1[CH];
+                load_acc(c, r0, r1);
+#pragma unroll
+                for (int j = 0; j < CH; ++j) {
+                    __stcg(wsp + (size_t)(c * CH + j) * GEMM_BM + n_local, __uint_as_float(r0[j]));
+                    if (NA == 2) __stcg(wsp + (size_t)(BT + c * CH + j) * GEMM_BM + n_local, __uint_as_float(r1[j]));
+                }
+            }
+            __threadfence();
+            asm volatile("bar.sync 1, 128;" ::: "memory");
+            if (threadIdx.x == 64) s_last = (atomicAdd(p.ws_counters + tile, 1u) == (unsigned)(S - 1)) ? 1 : 0;
+            asm volatile("bar.sync 1, 128;" ::: "memory");
+            if (s_last) {
+                __threadfence();
+                const float* base = p.ws + (tile * S * NA) * (size_t)BT * GEMM_BM;
+#pragma unroll 1
+                for (int c = 0; c < BT / CH; ++c) {
+                    if (t0 + c * CH >= t_end) break;
+                    uint32_t r0[CH], r1[CH];
+#pragma unroll
+                    for (int j = 0; j < CH; ++j) {
+                        float a0 = 0.f, a1 = 0.f;
+                        for (int z = 0; z < S; ++z) {      // fixed order: the result does not depend on which split finished last
+                            const float* pz = base + (size_t)z * NA * BT * GEMM_BM;
+                            a0 += __ldcg(pz + (size_t)(c * CH + j) * GEMM_BM + n_local);
+                            if (NA == 2) a1 += __ldcg(pz + (size_t)(BT + c * CH + j) * GEMM_BM + n_local);
+                        }
+                        r0[j] = __float_as_uint(a0);
+                        r1[j] = __float_as_uint(a1);
+                    }
+                    run_epilogue(c, r0, r1);
+                }
+                if (threadIdx.x == 64) p.ws_counters[tile] = 0;    // ready for the next launch
             }
         }
     }
@@ -319,7 +377,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tm_w0, const __grid_cons
             *p.coll.rs_done = 0;
             __threadfence_system();
             for (int pr = 0; pr < p.coll.rs_tp; ++pr)
-                asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p.coll.rs_peer_flags[pr] + p.coll.rs_rank), "r"(p.coll.rs_epoch) : "memory");
+                asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p.coll.rs_peer_flags[pr] + p.coll.rs_rank), "r"(sp_epoch(p.coll.step, p.coll.rs_epoch)) : "memory");
         }
     }
 }
@@ -373,13 +431,36 @@ static int launch_gemm(const CUtensorMap& tw0, const CUtensorMap& tw1, const CUt
     return 0;
 }
 
+// Split-K through the workspace for the epilogues that cannot reduce across CTAs themselves: skinny problems (decode batches,
+// narrow tensor-parallel shards) have fewer 128-row tiles than the machine has SMs, and a CTA per tile streams its weight rows at
+// a fraction of the HBM rate.  Workspace layout: 4096 tile counters (zero-initialised by the owner, self-resetting), then
+// [tile][split][accumulator][BT][128] fp32 partials.
+constexpr size_t GEMM_WS_COUNTERS = 4096;
+static int auto_split_ws(int epilogue, int split_k, long tiles, int total_kb, int na, int bt, void* ws, size_t ws_bytes, GemmParams& p) {
+    if (split_k > 0 || ws == nullptr || tiles <= 0 || tiles > (long)GEMM_WS_COUNTERS) return 1;
+    static int enabled = -1;
+    if (enabled < 0) { const char* e = getenv("DLP_GEMM_SPLITK"); enabled = (e && e[0] == '0') ? 0 : 1; }
+    if (!enabled) return 1;
+    int s = sm_count() / (int)tiles;
+    if (s > 8) s = 8;
+    while (s > 1 && total_kb / s < 4) --s;
+    const size_t per = (size_t)na * bt * GEMM_BM * sizeof(float);
+    while (s > 1 && GEMM_WS_COUNTERS * 4 + (size_t)tiles * s * per > ws_bytes) --s;
+    if (s <= 1) return 1;
+    p.ws_counters = reinterpret_cast<unsigned*>(ws);
+    p.ws = reinterpret_cast<float*>(reinterpret_cast<uint8_t*>(ws) + GEMM_WS_COUNTERS * 4);
+    return s;
+}
+
 // Y[T,N] (op)= X[T,K] . W0[N,K]^T  (and W1 for SwiGLU).  X/W are fp16 (is_bf16=0) or bf16 (is_bf16=1).
 int gemm_f16(const void* w0, const void* w1, int ldw, const void* x, int ldx, void* y, int ldy, int T, int N, int K,
-             int epilogue, int is_bf16, int split_k, cudaStream_t stream, const GemmCollective* coll, const GemmGroup* grp) {
+             int epilogue, int is_bf16, int split_k, cudaStream_t stream, const GemmCollective* coll, const GemmGroup* grp, void* ws,
+             size_t ws_bytes) {
     // grouped: N = output features of ONE expert, w0/w1 = stacks of all experts (rows_total = what the tensor map must cover)
     DLP_REQUIRE(T > 0 && N > 0 && K > 0, "gemm: empty problem T=%d N=%d K=%d", T, N, K);
     DLP_REQUIRE(grp == nullptr || (grp->tile_expert && grp->tile_row0 && grp->tile_rows && grp->n_tiles && grp->max_tiles > 0 && split_k <= 1 &&
                                    epilogue != EPI_RS_PUSH_F32 && epilogue != EPI_ATOMIC_ADD_F32), "gemm: bad grouped descriptor");
+    if (grp && split_k == 1) { ws = nullptr; ws_bytes = 0; }
     DLP_REQUIRE(K % GEMM_BK == 0, "gemm: K=%d must be a multiple of %d", K, GEMM_BK);
     const int na = (epilogue == EPI_SWIGLU_F16) ? 2 : 1;
     DLP_REQUIRE(na == 1 || w1 != nullptr, "gemm: SwiGLU epilogue needs the up-projection weight");
@@ -387,26 +468,30 @@ int gemm_f16(const void* w0, const void* w1, int ldw, const void* x, int ldx, vo
     int splits = split_k;
     if (splits <= 0) {  // auto: fill the machine when the epilogue can reduce across CTAs
         splits = 1;
-        if (epilogue == EPI_ATOMIC_ADD_F32) {
+        if (epilogue == EPI_ATOMIC_ADD_F32 && ws == nullptr) {   // (with a workspace the deterministic fix-up split below is used instead)
             const int bt_guess = T <= 16 ? 16 : T <= 32 ? 32 : T <= 64 ? 64 : T <= 128 ? 128 : 256;
             const long tiles = (long)((N + GEMM_BM - 1) / GEMM_BM) * ((T + bt_guess - 1) / bt_guess);
             const int sms = sm_count();
             while (tiles * splits * 2 <= sms && total_kb / (splits * 2) >= 8) splits *= 2;
         }
     }
-    DLP_REQUIRE(splits == 1 || epilogue == EPI_ATOMIC_ADD_F32, "gemm: split-K needs the atomic-add epilogue");
+    DLP_REQUIRE(splits == 1 || epilogue == EPI_ATOMIC_ADD_F32, "gemm: split-K needs the atomic-add epilogue or a workspace");
     if (splits > total_kb) splits = total_kb;
     GemmParams p;
     memset(&p, 0, sizeof(p));
     if (coll) p.coll = *coll;
     DLP_REQUIRE(epilogue != EPI_RS_PUSH_F32 || (coll && coll->rs_rows > 0 && coll->rs_done && coll->rs_tp >= 1 && coll->rs_tp <= 8 && splits == 1),
-                "gemm: the reduce-scatter epilogue needs a collective descriptor and no split-K");
+                "gemm: the reduce-scatter epilogue needs a collective descriptor and no atomic split-K");
     p.y = y; p.T = T; p.N = N; p.K = K; p.ldy = ldy; p.epilogue = epilogue;
+    if (grp) p.grp = *grp;
+    const int bt = grp ? grp->bt : (T <= 16 ? 16 : T <= 32 ? 32 : T <= 64 ? 64 : T <= 128 ? 128 : 256);
+    if (splits == 1)
+        splits = auto_split_ws(epilogue, split_k, (long)((N + GEMM_BM - 1) / GEMM_BM) * (grp ? grp->max_tiles : (T + bt - 1) / bt), total_kb, na, bt,
+                               ws, ws_bytes, p);
     p.k_blocks_per_split = (total_kb + splits - 1) / splits;
     splits = (total_kb + p.k_blocks_per_split - 1) / p.k_blocks_per_split;
-    if (grp) p.grp = *grp;
+    if (splits == 1) { p.ws = nullptr; p.ws_counters = nullptr; }
 
-    const int bt = grp ? grp->bt : (T <= 16 ? 16 : T <= 32 ? 32 : T <= 64 ? 64 : T <= 128 ? 128 : 256);
     DLP_REQUIRE(bt == 16 || bt == 32 || bt == 64 || bt == 128 || bt == 256, "gemm: token tile %d", bt);
     const uint64_t w_rows = grp ? (uint64_t)grp->rows_per_expert * grp->n_expert : (uint64_t)N;   // grouped: the map spans the whole stack
     CUtensorMap tw0, tw1, tx;
@@ -435,7 +520,7 @@ int gemm_f16(const void* w0, const void* w1, int ldw, const void* x, int ldx, vo
 
 // Y[T,N] (op)= X[T,K] . dequant(W)[N,K]^T with the block-quant decode fused into the A-operand producer.
 int gemm_quant(const QWeight& w0, const QWeight* w1, int wtype, const void* x, int ldx, void* y, int ldy, int T, int epilogue,
-               int split_k, cudaStream_t stream, const GemmCollective* coll, const GemmGroup* grp) {
+               int split_k, cudaStream_t stream, const GemmCollective* coll, const GemmGroup* grp, void* ws, size_t ws_bytes) {
     // grouped: w0 / w1 describe the stack of all experts (w0.N = n_expert * rows_per_expert); one expert's width tiles the grid
     const int N = grp ? grp->rows_per_expert : w0.N, K = w0.K;
     DLP_REQUIRE(T > 0 && N > 0 && K > 0 && K % 256 == 0, "gemm_quant: bad problem T=%d N=%d K=%d", T, N, K);
@@ -448,25 +533,29 @@ int gemm_quant(const QWeight& w0, const QWeight* w1, int wtype, const void* x, i
     int splits = split_k;
     if (splits <= 0) {
         splits = 1;
-        if (epilogue == EPI_ATOMIC_ADD_F32) {
+        if (epilogue == EPI_ATOMIC_ADD_F32 && ws == nullptr) {   // (with a workspace the deterministic fix-up split below is used instead)
             const int bt_guess = T <= 16 ? 16 : T <= 32 ? 32 : T <= 64 ? 64 : T <= 128 ? 128 : 256;
             const long tiles = (long)((N + GEMM_BM - 1) / GEMM_BM) * ((T + bt_guess - 1) / bt_guess);
             const int sms = sm_count();
             while (tiles * splits * 2 <= sms && total_kb / (splits * 2) >= 8) splits *= 2;
         }
     }
-    DLP_REQUIRE(splits == 1 || epilogue == EPI_ATOMIC_ADD_F32, "gemm_quant: split-K needs the atomic-add epilogue");
+    DLP_REQUIRE(splits == 1 || epilogue == EPI_ATOMIC_ADD_F32, "gemm_quant: split-K needs the atomic-add epilogue or a workspace");
     if (splits > total_kb) splits = total_kb;
     GemmParams p;
     memset(&p, 0, sizeof(p));
     if (coll) p.coll = *coll;
     DLP_REQUIRE(epilogue != EPI_RS_PUSH_F32 || (coll && coll->rs_rows > 0 && coll->rs_done && coll->rs_tp >= 1 && coll->rs_tp <= 8 && splits == 1),
-                "gemm: the reduce-scatter epilogue needs a collective descriptor and no split-K");
+                "gemm: the reduce-scatter epilogue needs a collective descriptor and no atomic split-K");
     p.y = y; p.T = T; p.N = N; p.K = K; p.ldy = ldy; p.epilogue = epilogue;
-    p.k_blocks_per_split = (total_kb + splits - 1) / splits;
-    splits = (total_kb + p.k_blocks_per_split - 1) / p.k_blocks_per_split;
     if (grp) p.grp = *grp;
     const int bt = grp ? grp->bt : (T <= 16 ? 16 : T <= 32 ? 32 : T <= 64 ? 64 : T <= 128 ? 128 : 256);
+    if (splits == 1)
+        splits = auto_split_ws(epilogue, split_k, (long)((N + GEMM_BM - 1) / GEMM_BM) * (grp ? grp->max_tiles : (T + bt - 1) / bt), total_kb, na, bt,
+                               ws, ws_bytes, p);
+    p.k_blocks_per_split = (total_kb + splits - 1) / splits;
+    splits = (total_kb + p.k_blocks_per_split - 1) / p.k_blocks_per_split;
+    if (splits == 1) { p.ws = nullptr; p.ws_counters = nullptr; }
     CUtensorMap tx;
     int rc;
     if ((rc = make_tmap_2d(&tx, x, 0, T, K, ldx, bt))) return rc;

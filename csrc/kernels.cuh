@@ -27,7 +27,8 @@ struct ArOut {                // producer: store this rank's partial rows into e
     const int* epoch;
     int rank, tp;
 };
-// Token exchange for sharded greedy sampling: slots [2 parities][tp][AR_MAX_T] of uint64, 0 = empty.
+// Token exchange for sharded greedy sampling: slots [2 parities][tp][TOKX_MAX_R] of uint64, 0 = empty.
+constexpr int TOKX_MAX_R = 64;
 struct TokX {
     unsigned long long* peer_slots[8];
     unsigned long long* mc_slots;
@@ -73,7 +74,13 @@ struct GemmCollective {
     unsigned* rs_done;
     int rs_rows, rs_rank, rs_tp;
     uint32_t rs_epoch;
+    // Epochs are `*step * SP_EPOCH_STRIDE + <the value above>` when `step` is given: the step counter lives on the device (bumped once
+    // per forward pass), the values above are then positions inside the step - launch-time constants, so a captured CUDA graph
+    // stays valid from step to step.  step == nullptr: the values above are absolute epochs.
+    const uint32_t* step;
 };
+constexpr uint32_t SP_EPOCH_STRIDE = 4096;
+__device__ __forceinline__ uint32_t sp_epoch(const uint32_t* step, uint32_t v) { return step ? *step * SP_EPOCH_STRIDE + v : v; }
 
 // Reduce-scatter consumer + RMSNorm + all-gather producer (one CTA per owned token row), see comm.cu.
 struct RsNormAg {
@@ -89,6 +96,7 @@ struct RsNormAg {
     unsigned* done;
     int* error;
     int rank, tp, rows, E;
+    const uint32_t* step;        // see GemmCollective::step
 };
 int rs_norm_ag(const RsNormAg& a, cudaStream_t s);
 
@@ -127,9 +135,10 @@ struct GemmGroup {
 int gemv(const GemvParams& p, int wtype, cudaStream_t stream);
 int gemm_f16(const void* w0, const void* w1, int ldw, const void* x, int ldx, void* y, int ldy, int T, int N, int K,
              int epilogue, int is_bf16, int split_k, cudaStream_t stream, const GemmCollective* coll = nullptr,
-             const GemmGroup* grp = nullptr);
+             const GemmGroup* grp = nullptr, void* ws = nullptr, size_t ws_bytes = 0);
 int gemm_quant(const QWeight& w0, const QWeight* w1, int wtype, const void* x, int ldx, void* y, int ldy, int T, int epilogue,
-               int split_k, cudaStream_t stream, const GemmCollective* coll = nullptr, const GemmGroup* grp = nullptr);
+               int split_k, cudaStream_t stream, const GemmCollective* coll = nullptr, const GemmGroup* grp = nullptr, void* ws = nullptr,
+               size_t ws_bytes = 0);
 // MoE routing plan + data movement around the grouped GEMMs (moe.cu)
 int moe_route_ex(const float* logits, int ld, int T, int n_expert, int top_k, int renorm, int* ids, float* w, cudaStream_t s);
 int moe_plan(const int* ids, int n_assign, int n_expert, int bt, int* pos, int* src, int* bounds, int* tile_expert, int* tile_row0,

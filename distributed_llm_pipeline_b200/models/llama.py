@@ -150,7 +150,7 @@ class LlamaEngine:
         self._seq_sampling: dict[int, tuple] = {}   # per-sequence overrides of self.sampling (set_seq_sampling)
         self.max_graphs = int(os.environ.get("DLP_MAX_GRAPHS", "24"))
         v0, v1 = weights.vocab_range
-        self.logits = torch.zeros(max_seqs, v1 - v0, dtype=f32, device=dev) if last_stage else None
+        self.logits = torch.zeros(max(max_seqs, 1), v1 - v0, dtype=f32, device=dev) if last_stage else None
         self.attn_splits = attn_splits if attn_splits is not None else (16 if dev.type == "cuda" else 1)
         ns = self.attn_splits
         self.attn_ws = (torch.zeros(max_seqs * self.Hq * ns * self.D, dtype=f32, device=dev),
@@ -529,13 +529,14 @@ class LlamaEngine:
         return {"model": self.w.nbytes(), "kv_cache": self.kv.bytes(), "compute": act,
                 "graphs": len(self._graphs), "device": str(self.device)}
 
-    def _forward_sp(self, T: int, attn_fn, logits_row: int | None):
+    def _forward_sp(self, T: int, attn_fn, logits_row: int | None, local_logits: bool = False):
         """Tensor-parallel forward for T > 4 tokens in the sequence-parallel layout (parallel/fused.py): the residual
         stream is sharded by token rows; every row-parallel GEMM pushes its partial tiles to the owner ranks from its
         epilogue (GEMM -> reduce-scatter), the owners fold + RMSNorm + push fp16 rows to everyone (all-gather), and the
         next column-parallel GEMM's TMA producer consumes the gathered rows as their flags arrive.  No NCCL call."""
         c, cfg, w = self.comm, self.cfg, self.w
         tp, rank = c.tp_size, c.tp_rank
+        c.begin_sp_step()
         Tp = (T + tp - 1) // tp * tp
         rows = Tp // tp
         r0 = rank * rows
@@ -573,6 +574,8 @@ class LlamaEngine:
         if self.last_stage:   # logits for every row (batched decode): all rows of the gathered, normalised stream
             c.sp_norm_ag(hs, rows, w.out_norm, cfg.rms_eps, g=0, red=pending)
             lg = c.sp_gemm(w.lm_head, c.sp_gather_view(0, Tp), E, T, rows, 1, y=self.logits[:T], x_from_g=0)
+            if local_logits:      # the caller finishes with the sharded arg-max: no gather
+                return lg
             return c.allgather_logits(lg, w.vocab_range, cfg.vocab_size)
         # pipeline hand-off: fold the last reduction, then rebuild the full [T, E] stream for the next stage
         c.sp_norm_ag(hs, rows, None, cfg.rms_eps, g=None, red=pending)
@@ -707,7 +710,11 @@ class LlamaEngine:
         sp = self.sp_ok and B > 4
         if sp:   # batched decode in the sequence-parallel layout (embedding happens per token shard inside)
             self.tokens[:B].copy_(self.next_tok[:B])
-            lg = self._forward_sp(B, self._attn_decode, None)
+            greedy = sample and self._greedy_now and self.last_stage
+            lg = self._forward_sp(B, self._attn_decode, None, local_logits=greedy)
+            if greedy:
+                self.comm.argmax_sharded(lg, self.w.vocab_range[0], self.next_tok[:B])
+                return
         else:
             if self.first_stage:
                 self._embed(B, self.next_tok[:B])  # input ids = previously sampled (or host-provided) tokens
@@ -742,14 +749,14 @@ class LlamaEngine:
             self.h[:B].copy_(hidden_in)
         moe_host = self.cfg.is_moe and not self._moe_grouped_ok(next(iter(self.w.layers.values())))   # routing through the host: no graph
         graphable = (use_graph and self.eval_callback is None and self.device.type == "cuda" and not moe_host
-                     and not getattr(self.comm, "no_graph", False)
-                     and not (self.sp_ok and B > 4))   # SP path passes host-side epochs as kernel arguments
+                     and not getattr(self.comm, "no_graph", False))   # (the sequence-parallel path is capturable too: its epochs are
+                                                                      #  positions inside the pass on top of a device-side counter)
         self._onepass_now = self.attn_onepass and max(self.seqs[sid].length for sid in sids) + 1 >= self.attn_onepass_min
         if sample and self.last_stage:
             self._sync_sampling(sids)
         # all rows greedy on the fused tensor-parallel path: sharded arg-max instead of gathering the logits (host-side fact, so
         # it is part of the graph key; at most one extra graph per batch size)
-        self._greedy_now = bool(sample and self.last_stage and self.fused_tp and B in (1, 2, 4) and
+        self._greedy_now = bool(sample and self.last_stage and self.fused_tp and (B in (1, 2, 4) or (self.sp_ok and 4 < B <= 64)) and
                                 os.environ.get("DLP_TP_ARGMAX", "1") == "1" and all(self._samp_host[sid][3] <= 0 for sid in sids))
         if graphable:
             # only the batch size, the output kind and the attention variant shape the graph (sampler parameters are device data)

@@ -131,11 +131,30 @@ def linear(w: DeviceWeight, x: torch.Tensor, out_mode: str = "f16", w_up: Device
         if scratch is None or scratch.numel() * scratch.element_size() < need:
             scratch = torch.empty(need, dtype=torch.uint8, device=x.device)
         _count(2 if w_up is not None else 1)
+    if scratch is None and not TWO_PASS_DEQUANT:
+        scratch = gemm_workspace(x.device)        # split-K workspace (skinny problems use every SM)
     sb = 0 if scratch is None else scratch.numel() * scratch.element_size()
     _lib.check(L.dlp_linear(w.ref(), up, x.data_ptr(), None, 0.0, out.data_ptr(), out.stride(0), mode, T, _p(scratch), sb,
                             _stream()), "linear")
     _count()
     return out
+
+
+_GEMM_WS: dict = {}
+GEMM_WS_BYTES = int(_os.environ.get("DLP_GEMM_WS_MB", "64")) << 20
+
+
+def gemm_workspace(device) -> torch.Tensor | None:
+    """Per-device split-K workspace of the tcgen05 GEMM: 16 KB of tile counters (zero once; they reset themselves) + partial tiles.
+    One buffer serves every GEMM of a device because GEMM launches on a stream never overlap.  DLP_GEMM_WS_MB=0 disables split-K."""
+    if GEMM_WS_BYTES <= 0:
+        return None
+    key = str(device)
+    ws = _GEMM_WS.get(key)
+    if ws is None:
+        ws = torch.zeros(GEMM_WS_BYTES + 16384, dtype=torch.uint8, device=device)
+        _GEMM_WS[key] = ws
+    return ws
 
 
 def gemm_f16(w: torch.Tensor, x: torch.Tensor, out: torch.Tensor, epilogue: int = 0, w_up: torch.Tensor | None = None,
@@ -474,10 +493,11 @@ def linear_grouped(w: DeviceWeight, xs: torch.Tensor, out: torch.Tensor, out_mod
     lib = _lib.load()
     lib.dlp_linear_grouped.restype = C.c_int
     lib.dlp_linear_grouped.argtypes = [C.POINTER(_lib.dlp_weight), C.POINTER(_lib.dlp_weight), C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int,
-                                       C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p]
+                                       C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p]
+    ws = gemm_workspace(xs.device)
     _lib.check(lib.dlp_linear_grouped(w.ref(), w_up.ref() if w_up is not None else None, xs.data_ptr(), out.data_ptr(), out.stride(0),
-                                      _OUT[out_mode], xs.shape[0], n_expert, rows_per_expert, token_tile, C.byref(plan.c), _stream()),
-               "linear_grouped")
+                                      _OUT[out_mode], xs.shape[0], n_expert, rows_per_expert, token_tile, C.byref(plan.c), _p(ws),
+                                      0 if ws is None else ws.numel(), _stream()), "linear_grouped")
     _count()
     return out
 

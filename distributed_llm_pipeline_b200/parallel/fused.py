@@ -29,6 +29,7 @@ from ..ops import lib as _lib
 from .comm import NcclComm
 
 MAX_T = 4  # token rows per site in the fused path
+TOKX_MAX_R = 64  # rows of the sharded arg-max exchange (csrc/kernels.cuh)
 
 
 AR_EMPTY = 0x80000000  # bit pattern of -0.0f: "not here yet" (csrc/kernels.cuh)
@@ -51,7 +52,8 @@ class dlp_tokx(C.Structure):
 class dlp_gemm_coll(C.Structure):
     _fields_ = [("x_flags", C.c_void_p), ("x_rows_per_src", C.c_int32), ("x_epoch", C.c_uint32), ("error", C.c_void_p),
                 ("rs_peer_buf", C.c_void_p * 8), ("rs_peer_flags", C.c_void_p * 8), ("rs_done", C.c_void_p),
-                ("rs_rows", C.c_int32), ("rs_rank", C.c_int32), ("rs_tp", C.c_int32), ("rs_epoch", C.c_uint32)]
+                ("rs_rows", C.c_int32), ("rs_rank", C.c_int32), ("rs_tp", C.c_int32), ("rs_epoch", C.c_uint32), ("step", C.c_void_p),
+                ("ws", C.c_void_p), ("ws_bytes", C.c_size_t)]
 
 
 class dlp_rs_norm_ag_desc(C.Structure):
@@ -59,7 +61,7 @@ class dlp_rs_norm_ag_desc(C.Structure):
                 ("pad0", C.c_uint32), ("norm_w", C.c_void_p), ("eps", C.c_float), ("pad1", C.c_uint32),
                 ("ag_peer_buf", C.c_void_p * 8), ("ag_peer_flags", C.c_void_p * 8), ("ag_epoch", C.c_uint32), ("pad2", C.c_uint32),
                 ("done", C.c_void_p), ("error", C.c_void_p), ("rank", C.c_int32), ("tp", C.c_int32), ("rows", C.c_int32),
-                ("E", C.c_int32)]
+                ("E", C.c_int32), ("step", C.c_void_p)]
 
 
 class FusedComm(NcclComm):
@@ -107,7 +109,7 @@ class FusedComm(NcclComm):
         self.E, self.n_sites = n_embd, n_sites
         self.site_stride = 2 * tp * MAX_T * n_embd * 4          # [2 parities][tp][MAX_T][E] fp32
         self.tok_off = n_sites * self.site_stride                # token exchange slots: uint64 [2][tp][MAX_T]
-        self.total_bytes = self.tok_off + ((2 * tp * MAX_T * 8 + 255) // 256) * 256
+        self.total_bytes = self.tok_off + ((2 * tp * TOKX_MAX_R * 8 + 255) // 256) * 256
 
     def _alloc_symmetric(self, nbytes: int):
         """(local base, [peer bases], multicast base or 0).  torch's symmetric memory is tried first because it also binds an NVLS
@@ -165,7 +167,8 @@ class FusedComm(NcclComm):
         st = torch.cuda.current_stream().cuda_stream
         _lib.check(self.lib.dlp_fill_u32(self.base, self.tok_off // 4, AR_EMPTY, st), "fill")
         _lib.check(self.lib.dlp_fill_u32(self.base + self.tok_off, (self.total_bytes - self.tok_off) // 4, 0, st), "fill")
-        self.epoch = torch.zeros(1, dtype=torch.int32, device=self.device)
+        self.epoch = torch.zeros(1, dtype=torch.int32, device=self.device)       # all-reduce sites: bumped once per fused decode step
+        self.tok_epoch = torch.zeros(1, dtype=torch.int32, device=self.device)   # token exchange: bumped before every sharded arg-max
         self.error = torch.zeros(1, dtype=torch.int32, device=self.device)
         self._in, self._out, self._tokx = {}, {}, None
         torch.cuda.synchronize()
@@ -247,18 +250,21 @@ class FusedComm(NcclComm):
             d = dlp_tokx()
             emu = getattr(self, "emulated", False)
             for r in range(self.tp_size):
-                d.peer_slots[r] = self.peers[r] + self.tok_off + (r * MAX_T * 8 if emu else 0)
+                d.peer_slots[r] = self.peers[r] + self.tok_off + (r * TOKX_MAX_R * 8 if emu else 0)
             d.mc_slots = (self.mc_base + self.tok_off) if self.mc_base else None
             d.slots = self.base + self.tok_off
-            d.epoch, d.error = self.epoch.data_ptr(), self.error.data_ptr()
-            d.rank, d.tp = self.tp_rank, self.tp_size
+            d.epoch, d.error = self.tok_epoch.data_ptr(), self.error.data_ptr()   # (own counter: the parities of the all-reduce
+            d.rank, d.tp = self.tp_rank, self.tp_size                             #  sites must only advance with steps that use them)
             self._tokx = d
         return self._tokx
 
     def argmax_sharded(self, logits: torch.Tensor, v0: int, out: torch.Tensor) -> torch.Tensor:
-        """Global arg-max over vocabulary-sharded logits [B, V_local] (B <= 4): the same token id on every rank, in one launch."""
+        """Global arg-max over vocabulary-sharded logits [B, V_local] (B <= 64): the same token id on every rank, in one launch."""
         from ..ops import api as ops
         B, V = logits.shape
+        st = torch.cuda.current_stream().cuda_stream
+        _lib.check(self.lib.dlp_bump(self.tok_epoch.data_ptr(), st), "bump")
+        ops._count()
         _lib.check(self.lib.dlp_argmax_tp(logits.data_ptr(), B, V, logits.stride(0), v0, C.byref(self.tokx()), out.data_ptr(),
                                           torch.cuda.current_stream().cuda_stream), "argmax_tp")
         ops._count()
@@ -297,9 +303,21 @@ class FusedComm(NcclComm):
         dist.barrier(group=self.group)
 
     def _sp_state(self):
-        self.g_epoch, self.r_epoch = [0, 0], [0, 0]
+        self.g_epoch, self.r_epoch = [0, 0], [0, 0]      # positions inside the current forward pass (see begin_sp_step)
         self.sp_done = torch.zeros(1, dtype=torch.int32, device=self.device)
+        self.sp_step = torch.zeros(1, dtype=torch.int32, device=self.device)   # forward-pass counter, bumped on the device
+        if not hasattr(self, "error"):
+            self.error = torch.zeros(1, dtype=torch.int32, device=self.device)
         self.sp_ready = True
+
+    def begin_sp_step(self):
+        """Start of a sequence-parallel forward pass (every rank, once per pass): the device-side pass counter advances and the
+        host-side epoch positions restart, so the epochs a launch carries are constants of its place in the pass - a captured
+        graph of the pass replays correctly at any later step."""
+        from ..ops import api as ops
+        _lib.check(self.lib.dlp_bump(self.sp_step.data_ptr(), torch.cuda.current_stream().cuda_stream), "bump")
+        ops._count()
+        self.g_epoch, self.r_epoch = [0, 0], [0, 0]
 
     def sp_tensor(self, g: int) -> torch.Tensor:
         """Zero-copy torch view ([Tmax, E] fp16) of this rank's gather buffer g."""
@@ -333,6 +351,7 @@ class FusedComm(NcclComm):
                 d.ag_peer_flags[r] = self.sp_peers[r] + self.sp_off["F"] + g * 64
         d.done, d.error = self.sp_done.data_ptr(), self.error.data_ptr()
         d.rank, d.tp, d.rows, d.E = self.tp_rank, self.tp_size, rows, self.sp_E
+        d.step = self.sp_step.data_ptr()
         _lib.check(self.lib.dlp_rs_norm_ag(C.byref(d), torch.cuda.current_stream().cuda_stream), "rs_norm_ag")
         ops._count()
 
@@ -343,6 +362,10 @@ class FusedComm(NcclComm):
         from ..ops import api as ops
         c = dlp_gemm_coll()
         c.error = self.error.data_ptr()
+        c.step = self.sp_step.data_ptr()
+        ws = ops.gemm_workspace(self.device)     # split-K workspace: a narrow shard has too few 128-row tiles to fill the SMs
+        if ws is not None:
+            c.ws, c.ws_bytes = ws.data_ptr(), ws.numel()
         if x_from_g is not None:
             c.x_flags = self.sp_base + self.sp_off["F"] + x_from_g * 64
             c.x_rows_per_src, c.x_epoch = rows, self.g_epoch[x_from_g]
@@ -397,5 +420,7 @@ class FusedComm(NcclComm):
         return super().allgather_logits(logits, vocab_range, vocab_size)
 
     def check_error(self):
+        if not getattr(self, "ready", False):      # never set up (e.g. a MoE model: its engine uses the NCCL entry points)
+            return
         if int(self.error.item()):
             raise RuntimeError("fused all-reduce: a peer did not signal within the timeout (ranks diverged or died)")

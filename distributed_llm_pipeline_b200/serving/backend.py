@@ -155,6 +155,8 @@ def main(argv=None):
     a = ap.parse_args(argv)
     maybe_reexec(a, "distributed_llm_pipeline_b200.serving.backend", argv)
     sched, info, logs = build_service(a.model, a.device, a.ctx_size, a.parallel, a.batch_size, lora=lora_from_args(a), **service_kwargs(a))
+    if not a.no_warmup:
+        logs.append(f"warm-up: decode graphs for 1..{sched.n_slots} sequences captured in {sched.warmup():.2f} s\n")
     for l in logs:
         sys.stderr.write(l)
     sys.stderr.flush()

@@ -665,6 +665,7 @@ def add_parallel_args(ap):
     ap.add_argument("--rpc", default=os.environ.get("DLP_ARG_RPC"), help="comma separated host:port list of dlp-worker stages (CPU layer split)")
     ap.add_argument("--workers", type=int, default=0, help="launch this many local dlp-worker stages and use them (implies --rpc)")
     ap.add_argument("--worker-base-port", type=int, default=50052)
+    ap.add_argument("--no-warmup", action="store_true", help="skip the start-up warm-up (kernel set-up + decode-graph capture per batch size)")
 
 
 def build_service(model: str, device: str = "cuda", n_ctx: int = 2048, n_slots: int = 4, n_batch: int = 2048, page_size: int = 64,
@@ -804,6 +805,8 @@ def main(argv=None):
     if not a.model:
         ap.error("-m/--model or --models is required")
     sched, info, logs = build_service(a.model, a.device, a.ctx_size, a.parallel, a.batch_size, lora=lora_from_args(a), **service_kwargs(a))
+    if not a.no_warmup:
+        logs.append(f"warm-up: decode graphs for 1..{sched.n_slots} sequences captured in {sched.warmup():.2f} s\n")
     for l in logs:
         sys.stderr.write(l)
     sched.context_shift = a.context_shift

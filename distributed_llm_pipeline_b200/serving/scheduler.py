@@ -148,6 +148,28 @@ class Scheduler:
         self.context_shift = False          # --context-shift: slide the window instead of stopping at n_ctx
         self.log = log or (lambda s: None)
 
+    def warmup(self) -> float:
+        """Run one tiny prefill and one decode step per batch size before traffic arrives, so that kernel set-up and CUDA-graph
+        capture (one graph per batch size, both attention variants) are paid at start-up and not by the first requests - the
+        reference server warms its context up the same way (`common_init_from_params` warm-up run, common/common.cpp).
+        Works through any engine (the distributed one replays the calls on every rank).  Returns the seconds spent."""
+        eng = self.eng
+        if eng.device.type != "cuda":
+            return 0.0
+        t0 = time.time()
+        n = min(self.n_slots, eng.max_seqs)
+        sids = [eng.alloc_seq() for _ in range(n)]
+        try:
+            for s in sids:
+                eng.prefill(s, [self.tok.bos_id if 0 <= self.tok.bos_id < self.tok.n_vocab else 1, 5, 6, 7, 8, 9])
+            for B in range(1, n + 1):
+                eng.decode(sids[:B], torch.full((B,), 5, dtype=torch.int32), sample=True)
+            torch.cuda.synchronize()
+        finally:
+            for s in sids:
+                eng.free_seq(s)
+        return time.time() - t0
+
     # ---- submission -------------------------------------------------------------------------------
     def submit(self, req: Request) -> Request:
         req.id = next(self._ids)
@@ -447,10 +469,43 @@ class Scheduler:
         if self.eng.device.type == "cuda":
             torch.cuda.set_device(self.eng.device)
         while not self._stop:
-            if not self.step():
+            try:
+                idle = not self.step()
+            except Exception as e:  # noqa: BLE001 - an engine fault must not leave clients waiting on a dead thread
+                self._engine_fault(e)
+                continue
+            if idle:
                 with self.wake:
                     if not self.queue and not self._jobs and not self._stop:
                         self.wake.wait(timeout=0.05)
+
+    def _engine_fault(self, e: Exception):
+        """Fail every request in flight with the error.  A CUDA fault poisons the context for good: say so and leave, so that a
+        supervisor (dlp-orchestrator --spawn, systemd, ...) can restart the service instead of clients hanging forever."""
+        import traceback
+        msg = f"engine fault: {type(e).__name__}: {e}".split("\n")[0]
+        self.log(msg + "\n")
+        traceback.print_exc()
+        for s in self.slots:
+            if s.req is not None:
+                try:
+                    self._fail(s, msg)
+                except Exception:  # noqa: BLE001
+                    s.req.done.set()
+                    s.state, s.req = SlotState.IDLE, None
+        with self.lock:
+            pending, self.queue = list(self.queue), deque()
+        for req in pending:
+            req.finish_reason = "error"
+            self._emit(req, "error", msg)
+            self._emit(req, "done", "error")
+            req.done.set()
+        if "CUDA" in str(e) or "cuda" in type(e).__name__.lower() or "Accelerator" in type(e).__name__:
+            import os
+            import sys
+            sys.stderr.write("fatal device error: the engine service exits\n")
+            sys.stderr.flush()
+            os._exit(3)
 
     # ---- blocking convenience ------------------------------------------------------------------------------
     def generate(self, prompt, **kw) -> Request:

@@ -63,8 +63,12 @@ int dlp_gemm_f16(const void* w0, const void* w1, int ldw, const void* x, int ldx
                  int K, int epilogue, int is_bf16, int split_k, void* stream);
 
 /* Any-T linear layer on any supported weight type.  T<=4 (T in {1,2,4}) routes to dlp_gemv.  Larger T runs the tcgen05
- * GEMM; block-quantised weights are first decoded to fp16 into `scratch` (needs 2*N*K bytes per matrix, two matrices
- * for SwiGLU) - the caller owns that buffer.  x must be fp16 when T>4.
+ * GEMM with the block-quant decode fused into its operand producer.  `scratch` (optional, caller-owned, zero-initialised once,
+ * >= 16 KB + room for partial tiles; 64 MB covers every shape here) is the split-K workspace: when a problem has fewer 128-row
+ * tiles than the GPU has SMs (decode batches, narrow tensor-parallel shards) K is split, each split stores its fp32 partial tile
+ * there and the split that arrives last adds them in a fixed order (deterministic) and runs the epilogue.  With
+ * DLP_GEMM_DEQUANT_SCRATCH=1 (A/B aid) `scratch` instead receives the decoded fp16 weights (2*N*K bytes per matrix).  x must be
+ * fp16 when T>4.
  * ref: ggml_cuda_mul_mat dispatch (ggml-cuda/ggml-cuda.cu:2182-2265) incl. dequantise-then-cuBLAS (:1287-1294). */
 int dlp_linear(const dlp_weight* w0, const dlp_weight* w1, const void* x, const float* norm_w, float eps, void* y,
                int ldy, int out_mode, int T, void* scratch, size_t scratch_bytes, void* stream);
@@ -218,7 +222,7 @@ int dlp_moe_route_ex(const float* logits, int ld, int T, int n_expert, int top_k
 int dlp_moe_plan(const int32_t* ids, int n_assign, int n_expert, int token_tile, dlp_moe_plan_bufs* bufs, void* stream);
 int dlp_moe_gather(const void* x, int ldx, const int32_t* src, int top_k, int n_assign, int K, void* xs, void* stream);
 int dlp_linear_grouped(const dlp_weight* w0, const dlp_weight* w1, const void* xs, void* y, int ldy, int out_mode, int n_assign, int n_expert,
-                       int rows_per_expert, int token_tile, const dlp_moe_plan_bufs* bufs, void* stream);
+                       int rows_per_expert, int token_tile, const dlp_moe_plan_bufs* bufs, void* ws, size_t ws_bytes, void* stream);
 int dlp_moe_combine(const float* y, const int32_t* pos, const float* weights, int T, int top_k, int E, float* h, void* stream);
 
 /* ---- tensor-parallel decode with the all-reduce fused into the mat-vecs (NVLink stores from inside the kernels, no NCCL) ----
@@ -252,7 +256,9 @@ typedef struct dlp_ar_out {
     int32_t tp;
 } dlp_ar_out;
 /* Sharded greedy sampling: `logits` [R, V] are this rank's vocabulary shard (global ids v0 .. v0+V); every rank ends up with the
- * same global arg-max in out[R].  Slots: uint64 [2 parities][tp][DLP_AR_MAX_T], zero-initialised, symmetric like the buffers above. */
+ * same global arg-max in out[R] (R <= DLP_TOKX_MAX_R).  Slots: uint64 [2 parities][tp][DLP_TOKX_MAX_R], zero-initialised, symmetric
+ * like the buffers above. */
+#define DLP_TOKX_MAX_R 64
 typedef struct dlp_tokx {
     void* peer_slots[8];
     void* mc_slots;          /* multicast alias or NULL */
@@ -289,6 +295,10 @@ typedef struct dlp_gemm_coll {
     uint32_t* rs_done;           /* local scratch counter, zero-initialised */
     int32_t rs_rows, rs_rank, rs_tp;
     uint32_t rs_epoch;
+    const uint32_t* step;        /* optional device-resident forward-pass counter: epochs become *step * 4096 + the values above (their
+                                    position inside the pass), which keeps a captured CUDA graph valid from step to step */
+    void* ws;                    /* optional split-K workspace (see dlp_linear `scratch`): lets a narrow shard use all SMs */
+    size_t ws_bytes;
 } dlp_gemm_coll;
 typedef struct dlp_rs_norm_ag_desc {
     float* h_shard;
@@ -306,6 +316,7 @@ typedef struct dlp_rs_norm_ag_desc {
     uint32_t* done;
     int32_t* error;
     int32_t rank, tp, rows, E;
+    const uint32_t* step;        /* as in dlp_gemm_coll */
 } dlp_rs_norm_ag_desc;
 /* x fp16 [T, ldx]; epilogue: 0 f16, 1 f32, 2 atomic add f32, 3 SwiGLU f16 (w1 = up), 5 reduce-scatter push (y unused). */
 int dlp_gemm_sp(const dlp_weight* w0, const dlp_weight* w1, const void* x, int ldx, void* y, int ldy, int epilogue, int T,

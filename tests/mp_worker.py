@@ -82,7 +82,7 @@ def main():
     if comm is not None and getattr(comm, "fused", False):
         comm.check_error()
         if grid.rank == 0:
-            print(f"symmetric memory: {comm.symm_backend}, multicast {'on' if comm.mc_base else 'off'} {getattr(comm, 'symm_note', '')}")
+            print(f"symmetric memory: {getattr(comm, 'symm_backend', None)}, multicast {'on' if getattr(comm, 'mc_base', 0) else 'off'} {getattr(comm, 'symm_note', '')}")
     if not greedy_ok:
         worst = 1.0
     res = torch.tensor([worst], dtype=torch.float64)

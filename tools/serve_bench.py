@@ -40,8 +40,8 @@ def _request(host, port, path, body: bytes, on_data):
     s.close()
 
 
-def run_one(a, idx, out):
-    rnd = random.Random(1000 + idx)
+def run_one(a, idx, out, seed_off=0):
+    rnd = random.Random(1000 + idx + seed_off)
     toks = [rnd.randrange(3, a.vocab) for _ in range(a.prompt_tokens)]
     t0 = time.perf_counter()
     st = {"first": None, "n": 0, "last": t0}
@@ -88,11 +88,17 @@ def main():
     ap.add_argument("--prompt-tokens", type=int, default=128)
     ap.add_argument("-n", "--n-predict", type=int, default=64)
     ap.add_argument("--vocab", type=int, default=32000)
+    ap.add_argument("--warmup-rounds", type=int, default=1, help="unmeasured rounds at each concurrency level before the timed one")
     ap.add_argument("--tag", default="")
     ap.add_argument("-o", "--output", default="")
     a = ap.parse_args()
     rows = []
     for conc in [int(x) for x in a.concurrency.split(",")]:
+        for _ in range(a.warmup_rounds):      # both arms get the same treatment: first-use costs stay out of the timed round
+            out = [None] * conc
+            ts = [threading.Thread(target=run_one, args=(a, i, out, 10000)) for i in range(conc)]
+            [t.start() for t in ts]
+            [t.join() for t in ts]
         out = [None] * conc
         ts = [threading.Thread(target=run_one, args=(a, i, out)) for i in range(conc)]
         t0 = time.perf_counter()
