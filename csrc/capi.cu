@@ -193,25 +193,21 @@ int dlp_gemm_f16(const void* w0, const void* w1, int ldw, const void* x, int ldx
     return gemm_f16(w0, w1, ldw, x, ldx, y, ldy, T, N, K, epilogue, is_bf16, split_k, (cudaStream_t)stream);
 }
 
-int dlp_linear(const dlp_weight* w0, const dlp_weight* w1, const void* x, const float* norm_w, float eps, void* y,
-               int ldy, int out_mode, int T, void* scratch, size_t scratch_bytes, void* stream) {
+static int linear_impl(const dlp_weight* w0, const dlp_weight* w1, const void* x, const float* norm_w, float eps, void* y,
+                       int ldy, int out_mode, int T, void* scratch, size_t scratch_bytes, void* ws, size_t ws_bytes, void* stream) {
     DLP_REQUIRE(w0 && w0->base && x && y, "dlp_linear: null argument");
     if (T == 1 || T == 2 || T == 4) return dlp_gemv(w0, w1, x, norm_w, eps, y, ldy, out_mode, T, stream);
     DLP_REQUIRE(norm_w == nullptr, "dlp_linear: RMSNorm fusion is only available on the T<=4 mat-vec path");
     const int epi = out_mode == DLP_OUT_F16 ? 0 : out_mode == DLP_OUT_F32 ? 1 : out_mode == DLP_OUT_ADD_F32 ? 2 : 3;
     const int wt = w0->wtype;
     cudaStream_t s = (cudaStream_t)stream;
-    static int two_pass = -1;
-    if (two_pass < 0) { const char* e = getenv("DLP_GEMM_DEQUANT_SCRATCH"); two_pass = (e && e[0] == '1') ? 1 : 0; }
-    // (unless the two-pass dequant path owns it, `scratch` is the split-K workspace: 16 KB of zero-initialised tile counters
-    //  followed by room for the partial tiles; NULL = no split-K for the store epilogues)
-    void* ws = two_pass ? nullptr : scratch;
-    const size_t ws_bytes = two_pass ? 0 : scratch_bytes;
     if (wt == DLP_W_F16 || wt == DLP_W_BF16)
         return gemm_f16(w0->base, w1 ? w1->base : nullptr, w0->K, x, w0->K, y, ldy, T, w0->N, w0->K, epi,
                         wt == DLP_W_BF16, 0, s, nullptr, nullptr, ws, ws_bytes);
     // block-quantised: the decode is fused into the GEMM's A-operand producer (no scratch).  DLP_GEMM_DEQUANT_SCRATCH=1
     // selects the older two-pass path (decode to fp16 scratch, then the dense GEMM) for A/B runs.
+    static int two_pass = -1;
+    if (two_pass < 0) { const char* e = getenv("DLP_GEMM_DEQUANT_SCRATCH"); two_pass = (e && e[0] == '1') ? 1 : 0; }
     if (!two_pass) {
         const QWeight q0 = to_qw(w0);
         QWeight q1;
@@ -229,7 +225,16 @@ int dlp_linear(const dlp_weight* w0, const dlp_weight* w1, const void* x, const 
         rc = dequant_rows_f16(to_qw(w1), wt, nullptr, w1->N, (__half*)up, w1->K, s);
         if (rc) return rc;
     }
-    return gemm_f16(scratch, up, w0->K, x, w0->K, y, ldy, T, w0->N, w0->K, epi, 0, 0, s);
+    return gemm_f16(scratch, up, w0->K, x, w0->K, y, ldy, T, w0->N, w0->K, epi, 0, 0, s, nullptr, nullptr, ws, ws_bytes);
+}
+
+int dlp_linear(const dlp_weight* w0, const dlp_weight* w1, const void* x, const float* norm_w, float eps, void* y,
+               int ldy, int out_mode, int T, void* scratch, size_t scratch_bytes, void* stream) {
+    return linear_impl(w0, w1, x, norm_w, eps, y, ldy, out_mode, T, scratch, scratch_bytes, nullptr, 0, stream);
+}
+int dlp_linear_ws(const dlp_weight* w0, const dlp_weight* w1, const void* x, const float* norm_w, float eps, void* y,
+                  int ldy, int out_mode, int T, void* scratch, size_t scratch_bytes, void* ws, size_t ws_bytes, void* stream) {
+    return linear_impl(w0, w1, x, norm_w, eps, y, ldy, out_mode, T, scratch, scratch_bytes, ws, ws_bytes, stream);
 }
 
 int dlp_moe_route_ex(const float* logits, int ld, int T, int n_expert, int top_k, int renorm, int32_t* ids, float* weights, void* stream) {

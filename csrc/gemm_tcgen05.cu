@@ -437,7 +437,10 @@ static int launch_gemm(const CUtensorMap& tw0, const CUtensorMap& tw1, const CUt
 // [tile][split][accumulator][BT][128] fp32 partials.
 constexpr size_t GEMM_WS_COUNTERS = 4096;
 static int auto_split_ws(int epilogue, int split_k, long tiles, int total_kb, int na, int bt, void* ws, size_t ws_bytes, GemmParams& p) {
-    if (split_k > 0 || ws == nullptr || tiles <= 0 || tiles > (long)GEMM_WS_COUNTERS) return 1;
+    // Measured (profiles/r2_gemm_splitk_ab.txt): the fix-up pays for token tiles up to 32 (decode batches: +19 % at B = 8); for
+    // prefill-sized tiles the serial reload of 128 x 256 partials costs more than the idle SMs (54 k -> 29 k tok/s at pp512), and
+    // the residual-add epilogue reduces across CTAs with atomics at no extra cost.
+    if (split_k > 0 || ws == nullptr || tiles <= 0 || tiles > (long)GEMM_WS_COUNTERS || bt > 32 || epilogue == EPI_ATOMIC_ADD_F32) return 1;
     static int enabled = -1;
     if (enabled < 0) { const char* e = getenv("DLP_GEMM_SPLITK"); enabled = (e && e[0] == '0') ? 0 : 1; }
     if (!enabled) return 1;
@@ -468,7 +471,7 @@ int gemm_f16(const void* w0, const void* w1, int ldw, const void* x, int ldx, vo
     int splits = split_k;
     if (splits <= 0) {  // auto: fill the machine when the epilogue can reduce across CTAs
         splits = 1;
-        if (epilogue == EPI_ATOMIC_ADD_F32 && ws == nullptr) {   // (with a workspace the deterministic fix-up split below is used instead)
+        if (epilogue == EPI_ATOMIC_ADD_F32) {
             const int bt_guess = T <= 16 ? 16 : T <= 32 ? 32 : T <= 64 ? 64 : T <= 128 ? 128 : 256;
             const long tiles = (long)((N + GEMM_BM - 1) / GEMM_BM) * ((T + bt_guess - 1) / bt_guess);
             const int sms = sm_count();
@@ -533,7 +536,7 @@ int gemm_quant(const QWeight& w0, const QWeight* w1, int wtype, const void* x, i
     int splits = split_k;
     if (splits <= 0) {
         splits = 1;
-        if (epilogue == EPI_ATOMIC_ADD_F32 && ws == nullptr) {   // (with a workspace the deterministic fix-up split below is used instead)
+        if (epilogue == EPI_ATOMIC_ADD_F32) {
             const int bt_guess = T <= 16 ? 16 : T <= 32 ? 32 : T <= 64 ? 64 : T <= 128 ? 128 : 256;
             const long tiles = (long)((N + GEMM_BM - 1) / GEMM_BM) * ((T + bt_guess - 1) / bt_guess);
             const int sms = sm_count();

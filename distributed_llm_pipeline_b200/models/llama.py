@@ -151,6 +151,8 @@ class LlamaEngine:
         self.max_graphs = int(os.environ.get("DLP_MAX_GRAPHS", "24"))
         v0, v1 = weights.vocab_range
         self.logits = torch.zeros(max(max_seqs, 1), v1 - v0, dtype=f32, device=dev) if last_stage else None
+        if last_stage and self.comm.tp_size > 1 and hasattr(self.comm, "reserve_logits") and (v1 - v0) != cfg.vocab_size:
+            self.comm.reserve_logits(max_seqs, v1 - v0, f32, dev)     # before any graph is captured
         self.attn_splits = attn_splits if attn_splits is not None else (16 if dev.type == "cuda" else 1)
         ns = self.attn_splits
         self.attn_ws = (torch.zeros(max_seqs * self.Hq * ns * self.D, dtype=f32, device=dev),

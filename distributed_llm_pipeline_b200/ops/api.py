@@ -131,11 +131,13 @@ def linear(w: DeviceWeight, x: torch.Tensor, out_mode: str = "f16", w_up: Device
         if scratch is None or scratch.numel() * scratch.element_size() < need:
             scratch = torch.empty(need, dtype=torch.uint8, device=x.device)
         _count(2 if w_up is not None else 1)
-    if scratch is None and not TWO_PASS_DEQUANT:
-        scratch = gemm_workspace(x.device)        # split-K workspace (skinny problems use every SM)
     sb = 0 if scratch is None else scratch.numel() * scratch.element_size()
-    _lib.check(L.dlp_linear(w.ref(), up, x.data_ptr(), None, 0.0, out.data_ptr(), out.stride(0), mode, T, _p(scratch), sb,
-                            _stream()), "linear")
+    ws = gemm_workspace(x.device)                 # split-K workspace (skinny problems use every SM)
+    L.dlp_linear_ws.restype = C.c_int
+    L.dlp_linear_ws.argtypes = [C.POINTER(_lib.dlp_weight), C.POINTER(_lib.dlp_weight), C.c_void_p, C.c_void_p, C.c_float, C.c_void_p, C.c_int,
+                                C.c_int, C.c_int, C.c_void_p, C.c_size_t, C.c_void_p, C.c_size_t, C.c_void_p]
+    _lib.check(L.dlp_linear_ws(w.ref(), up, x.data_ptr(), None, 0.0, out.data_ptr(), out.stride(0), mode, T, _p(scratch), sb,
+                               _p(ws), 0 if ws is None else ws.numel(), _stream()), "linear")
     _count()
     return out
 

@@ -63,15 +63,19 @@ int dlp_gemm_f16(const void* w0, const void* w1, int ldw, const void* x, int ldx
                  int K, int epilogue, int is_bf16, int split_k, void* stream);
 
 /* Any-T linear layer on any supported weight type.  T<=4 (T in {1,2,4}) routes to dlp_gemv.  Larger T runs the tcgen05
- * GEMM with the block-quant decode fused into its operand producer.  `scratch` (optional, caller-owned, zero-initialised once,
- * >= 16 KB + room for partial tiles; 64 MB covers every shape here) is the split-K workspace: when a problem has fewer 128-row
- * tiles than the GPU has SMs (decode batches, narrow tensor-parallel shards) K is split, each split stores its fp32 partial tile
- * there and the split that arrives last adds them in a fixed order (deterministic) and runs the epilogue.  With
- * DLP_GEMM_DEQUANT_SCRATCH=1 (A/B aid) `scratch` instead receives the decoded fp16 weights (2*N*K bytes per matrix).  x must be
- * fp16 when T>4.
+ * GEMM with the block-quant decode fused into its operand producer; x must be fp16 when T>4.  `scratch` is only used with
+ * DLP_GEMM_DEQUANT_SCRATCH=1 (A/B aid: weights are first decoded to fp16 there, 2*N*K bytes per matrix, two for SwiGLU).
  * ref: ggml_cuda_mul_mat dispatch (ggml-cuda/ggml-cuda.cu:2182-2265) incl. dequantise-then-cuBLAS (:1287-1294). */
 int dlp_linear(const dlp_weight* w0, const dlp_weight* w1, const void* x, const float* norm_w, float eps, void* y,
                int ldy, int out_mode, int T, void* scratch, size_t scratch_bytes, void* stream);
+/* Same with a split-K workspace `ws` (caller-owned; its first 16 KB are tile counters that must be zero before the FIRST use and
+ * return to zero after every call; 64 MB + 16 KB covers every shape here).  When a problem has fewer 128-row tiles than the GPU
+ * has SMs (decode batches, narrow tensor-parallel shards) K is split, each split stores its fp32 partial tile in `ws`, and the
+ * split that arrives last adds the partials in split order (deterministic) and runs the epilogue - any epilogue, including
+ * the residual add.  Calls that share one `ws` must not overlap on the GPU.
+ * ref: mul_mat_q stream-k + mul_mat_q_stream_k_fixup (ggml-cuda/mmq.cuh:3459,3702). */
+int dlp_linear_ws(const dlp_weight* w0, const dlp_weight* w1, const void* x, const float* norm_w, float eps, void* y,
+                  int ldy, int out_mode, int T, void* scratch, size_t scratch_bytes, void* ws, size_t ws_bytes, void* stream);
 
 /* Decode rows of a weight matrix to fp32 / fp16 (row_ids == NULL => rows 0..n_rows-1).  Embedding gather + dequant.
  * ref: k_get_rows (ggml-cuda/getrows.cu), dequantize_block_* (convert.cu). */
