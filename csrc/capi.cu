@@ -377,6 +377,12 @@ int dlp_attn_paged_static(const void* q, const void* k_cache, const void* v_cach
     return attn_paged_static(p, D, (cudaStream_t)stream);
 }
 
+int dlp_attn_prefill_tc(const void* q, const void* k_cache, const void* v_cache, const int32_t* block_table_row, void* out, int T, int pos0,
+                        int Hq, int Hkv, int D, int page_size, int n_pages, int max_pages, void* stream) {
+    DLP_REQUIRE(q && k_cache && v_cache && block_table_row && out, "dlp_attn_prefill_tc: null argument");
+    return attn_prefill_tc((const __half*)q, (const __half*)k_cache, (const __half*)v_cache, block_table_row, (__half*)out, T, pos0, Hq, Hkv, D,
+                           page_size, n_pages, max_pages, (cudaStream_t)stream);
+}
 int dlp_attn_prefill(const void* q, const void* k_cache, const void* v_cache, const int32_t* block_table_row,
                      void* out, int T, int pos0, int Hq, int Hkv, int D, int page_size, void* stream) {
     DLP_REQUIRE(q && k_cache && v_cache && block_table_row && out, "dlp_attn_prefill: null argument");

@@ -182,4 +182,7 @@ int bump(int* ctr, cudaStream_t s);
 int attn_prefill(const __half* q, const __half* kc, const __half* vc, const int* bt_row, __half* out, int T, int pos0,
                  int Hq, int Hkv, int D, int page_size, cudaStream_t s);
 
+int attn_prefill_tc(const __half* q, const __half* kc, const __half* vc, const int* bt_row, __half* out, int T, int pos0, int Hq, int Hkv,
+                    int D, int page_size, int n_pages, int max_pages, cudaStream_t s);
+
 }  // namespace dlp

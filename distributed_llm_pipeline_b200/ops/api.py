@@ -311,8 +311,11 @@ def attn_decode_rope(qkv: torch.Tensor, inv_freq: torch.Tensor, k_cache: torch.T
     return out
 
 
+ATTN_PREFILL_IMPL = _os.environ.get("DLP_ATTN_PREFILL", "tc")     # "tc" = tcgen05 kernel, "mma" = the mma.sync FA-2 kernel (A/B, fallback)
+
+
 def attn_prefill(q: torch.Tensor, k_cache: torch.Tensor, v_cache: torch.Tensor, block_table_row: torch.Tensor, pos0: int,
-                 n_head: int, n_head_kv: int, head_dim: int, out: torch.Tensor | None = None) -> torch.Tensor:
+                 n_head: int, n_head_kv: int, head_dim: int, out: torch.Tensor | None = None, impl: str | None = None) -> torch.Tensor:
     """Causal attention of a T-token chunk at positions [pos0, pos0+T) of one sequence."""
     T = q.shape[0]
     if not native(q):
@@ -325,8 +328,21 @@ def attn_prefill(q: torch.Tensor, k_cache: torch.Tensor, v_cache: torch.Tensor, 
         return res
     if out is None:
         out = torch.empty(T, n_head * head_dim, dtype=torch.float16, device=q.device)
+    page = k_cache.shape[2]
+    impl = impl or ATTN_PREFILL_IMPL
+    if (impl == "tc" and page % 8 == 0 and 128 % page == 0 and q.is_contiguous() and q.shape[1] == n_head * head_dim
+            and k_cache.is_contiguous() and v_cache.is_contiguous()):
+        # tcgen05 / TMEM / TMA flash-prefill (csrc/attention_tc.cu)
+        L = _lib.load()
+        L.dlp_attn_prefill_tc.restype = C.c_int
+        L.dlp_attn_prefill_tc.argtypes = [C.c_void_p] * 5 + [C.c_int] * 8 + [C.c_void_p]
+        _lib.check(L.dlp_attn_prefill_tc(q.data_ptr(), k_cache.data_ptr(), v_cache.data_ptr(), block_table_row.data_ptr(), out.data_ptr(),
+                                         T, pos0, n_head, n_head_kv, head_dim, page, k_cache.shape[0], block_table_row.numel(), _stream()),
+                   "attn_prefill_tc")
+        _count()
+        return out
     _lib.check(_lib.load().dlp_attn_prefill(q.data_ptr(), k_cache.data_ptr(), v_cache.data_ptr(), block_table_row.data_ptr(),
-                                            out.data_ptr(), T, pos0, n_head, n_head_kv, head_dim, k_cache.shape[2],
+                                            out.data_ptr(), T, pos0, n_head, n_head_kv, head_dim, page,
                                             _stream()), "attn_prefill")
     _count()
     return out

@@ -169,6 +169,13 @@ int dlp_attn_paged_static(const void* q, const void* k_cache, const void* v_cach
 int dlp_attn_prefill(const void* q, const void* k_cache, const void* v_cache, const int32_t* block_table_row,
                      void* out, int T, int pos0, int Hq, int Hkv, int D, int page_size, void* stream);
 
+/* The same operation on the 5th-generation tensor cores: tcgen05 MMAs for Q.K^T and P.V with the score tile and the output
+ * accumulator in tensor memory, K / V pages fetched by TMA (V as the MN-major operand, straight from its cache layout).  q must be
+ * [T, Hq*D] contiguous; k_cache / v_cache are the whole [n_pages][Hkv][page_size][D] arrays (page_size a multiple of 8 dividing
+ * 128); block_table_row has max_pages entries.  ref: flash_attn_ext_f16 (fattn-mma-f16.cuh:38-104) is the mma.sync form. */
+int dlp_attn_prefill_tc(const void* q, const void* k_cache, const void* v_cache, const int32_t* block_table_row, void* out, int T, int pos0,
+                        int Hq, int Hkv, int D, int page_size, int n_pages, int max_pages, void* stream);
+
 /* Sampling on device, one row of fp32 logits per output token.  temp<=0 => greedy.
  * ref: llama_sampler chain top_k/top_p/min_p/temp/dist (llama.cpp/src/llama-sampling.cpp:1348-1918,1255), argmax.cu. */
 int dlp_argmax(const float* logits, int R, int V, int ld, int32_t* out, void* stream);

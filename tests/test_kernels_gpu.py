@@ -281,16 +281,18 @@ def test_attn_decode_rope_onepass(D, Hq, Hkv, neox, n_splits):
     assert torch.equal(kc.cpu()[untouched], kc_ref[untouched])          # nothing else in the cache was written
 
 
+@pytest.mark.parametrize("impl", ["tc", "mma"])
 @pytest.mark.parametrize("D,Hq,Hkv", [(128, 8, 2), (64, 4, 2)])
-@pytest.mark.parametrize("T,pos0", [(5, 0), (64, 0), (100, 37), (200, 64)])
-def test_attn_prefill_causal(D, Hq, Hkv, T, pos0):
-    page = 16
+@pytest.mark.parametrize("T,pos0,page", [(5, 0, 16), (64, 0, 16), (100, 37, 16), (200, 64, 16), (128, 0, 64), (300, 250, 64), (513, 1000, 64), (1, 400, 8)])
+def test_attn_prefill_causal(D, Hq, Hkv, T, pos0, page, impl):
+    """Both prefill-attention kernels (tcgen05/TMEM/TMA and the mma.sync FA-2 one) against fp32 attention over the same pages:
+    tiles that end inside a page, chunks that start mid-sequence, more than one 128-query tile, several 128-key tiles."""
     total = pos0 + T
     n_need = (total + page - 1) // page
     kc, vc = _fill_cache(n_need + 3, Hkv, page, D, seed=1)
     row = torch.randperm(n_need + 3)[:n_need].to(torch.int32).to(DEV)
     q = (torch.randn(T, Hq * D, device=DEV) / math.sqrt(D)).half()
-    out = ops.attn_prefill(q, kc, vc, row, pos0, Hq, Hkv, D)
+    out = ops.attn_prefill(q, kc, vc, row, pos0, Hq, Hkv, D, impl=impl)
     kv_len = torch.arange(pos0 + 1, pos0 + T + 1, dtype=torch.int32)
     ref = ops._attn_cpu(q.cpu(), kc.cpu(), vc.cpu(), row.cpu().view(1, -1).expand(T, -1), kv_len, Hq, Hkv, D)
     assert nmse(ref, out) < 5e-4
