@@ -751,8 +751,8 @@ class LlamaEngine:
             self.h[:B].copy_(hidden_in)
         moe_host = self.cfg.is_moe and not self._moe_grouped_ok(next(iter(self.w.layers.values())))   # routing through the host: no graph
         graphable = (use_graph and self.eval_callback is None and self.device.type == "cuda" and not moe_host
-                     and not getattr(self.comm, "no_graph", False))   # (the sequence-parallel path is capturable too: its epochs are
-                                                                      #  positions inside the pass on top of a device-side counter)
+                     and not getattr(self.comm, "no_graph", False)    # (the sequence-parallel path is capturable too: its epochs are
+                     and not (self.sp_ok and B > 4 and os.environ.get("DLP_SP_GRAPH", "1") == "0"))   # positions inside the pass on top of a device-side counter; DLP_SP_GRAPH=0: A/B)
         self._onepass_now = self.attn_onepass and max(self.seqs[sid].length for sid in sids) + 1 >= self.attn_onepass_min
         if sample and self.last_stage:
             self._sync_sampling(sids)

@@ -36,14 +36,20 @@ clocks() { nvidia-smi --query-gpu=index,clocks.sm,clocks.max.sm,power.draw,clock
 P4=$(gen "$M4" Q4_K_M)
 if [[ $ARMS == *ours* ]]; then
   C=$(clocks $OUT/cfg4_ours_clocks.csv)
-  timeout 900 $TR tools/dlp_bench.py -m "$P4" --pp $PP --tp $TP -p 512 -n 32 -r 2 --batch 1,8,32 -c 1024 -o jsonl > $OUT/cfg4_ours.jsonl 2> $OUT/cfg4_ours.err
-  echo "cfg4 ours rc=$?"; kill $C 2>/dev/null
+  timeout 300 $TR tools/dlp_bench.py -m "$P4" --pp $PP --tp $TP -p 512 -n 32 -r 2 --batch 1,8,32 -c 1024 -o jsonl > $OUT/cfg4_ours.jsonl 2> $OUT/cfg4_ours.err
+  RC=$?; echo "cfg4 ours rc=$RC"
+  if [[ $RC != 0 ]]; then   # retry without graph capture of the sequence-parallel batched path
+    tail -3 $OUT/cfg4_ours.err | cut -c1-300
+    DLP_SP_GRAPH=0 timeout 300 $TR tools/dlp_bench.py -m "$P4" --pp $PP --tp $TP -p 512 -n 32 -r 2 --batch 1,8,32 -c 1024 -o jsonl > $OUT/cfg4_ours.jsonl 2> $OUT/cfg4_ours_retry.err
+    echo "cfg4 ours (DLP_SP_GRAPH=0) rc=$?"
+  fi
+  kill $C 2>/dev/null
   cat $OUT/cfg4_ours.jsonl | cut -c1-400
 fi
 if [[ $ARMS == *ref* ]]; then
   for sm in layer row; do
     C=$(clocks $OUT/cfg4_ref_${sm}_clocks.csv)
-    CUDA_VISIBLE_DEVICES=$GPUS timeout 900 $REF/llama-batched-bench -m "$P4" -c 8192 -b 2048 -ub 512 -npp 16 -ntg 32 -npl 1,8,32 -ngl 99 -fa 1 -sm $sm --output-format jsonl \
+    CUDA_VISIBLE_DEVICES=$GPUS timeout 200 $REF/llama-batched-bench -m "$P4" -c 8192 -b 2048 -ub 512 -npp 16 -ntg 32 -npl 1,8,32 -ngl 99 -fa 1 -sm $sm --output-format jsonl \
       > $OUT/cfg4_ref_$sm.jsonl 2> $OUT/cfg4_ref_$sm.err
     echo "cfg4 ref -sm $sm rc=$?"; kill $C 2>/dev/null
     grep -h '{' $OUT/cfg4_ref_$sm.jsonl $OUT/cfg4_ref_$sm.err | grep n_kv | cut -c1-300
@@ -57,7 +63,7 @@ wait_port() {  # until GET /health answers 200 (llama-server binds its port befo
   python - "$1" <<'EOF2'
 import socket, sys, time
 port = int(sys.argv[1])
-for _ in range(1200):
+for _ in range(300):
     try:
         s = socket.create_connection(("127.0.0.1", port), timeout=2)
         s.sendall(b"GET /health HTTP/1.1\r\nHost: x\r\nConnection: close\r\n\r\n")
