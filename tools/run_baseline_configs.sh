@@ -6,7 +6,8 @@
 set -uo pipefail
 PP=${1:-2}; TP=${2:-4}; M4=${3:-llama-3-70b}; M5=${4:-mixtral-8x7b}; NL=${5:-0}; ARMS=${6:-ours,ref}
 N=$((PP * TP))
-OUT=gpurun_out; mkdir -p $OUT /tmp/dlp_models
+MD=${DLP_MODEL_DIR:-/tmp/dlp_models}; export DLP_MODEL_DIR=$MD
+OUT=gpurun_out; mkdir -p $OUT $MD
 TR="python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29611"
 REF=baseline/_ref/bin
 python baseline/reference.py > $OUT/cfg_ref_setup.log 2>&1
@@ -20,7 +21,7 @@ sys.path.insert(0, os.getcwd())
 from distributed_llm_pipeline_b200.gguf import write_synthetic_gguf
 from distributed_llm_pipeline_b200.models.config import preset
 name, ftype, nl = sys.argv[1], sys.argv[2], int(sys.argv[3])
-path = f"/tmp/dlp_models/{name}{'-%dL' % nl if nl else ''}-{ftype}.gguf"
+path = f"{os.environ['DLP_MODEL_DIR']}/{name}{'-%dL' % nl if nl else ''}-{ftype}.gguf"
 if not os.path.exists(path):
     t = time.time()
     write_synthetic_gguf(path + ".tmp", preset(name, **({"n_layer": nl} if nl else {})), ftype, seed=0)
@@ -32,7 +33,9 @@ EOF
 
 clocks() { nvidia-smi --query-gpu=index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap --format=csv,noheader -lms 500 > "$1" & echo $!; }
 
+ONLY=${ONLY:-45}
 # ---------------- config 4 ----------------
+if [[ $ONLY == *4* ]]; then
 P4=$(gen "$M4" Q4_K_M)
 if [[ $ARMS == *ours* ]]; then
   C=$(clocks $OUT/cfg4_ours_clocks.csv)
@@ -47,7 +50,8 @@ if [[ $ARMS == *ours* ]]; then
   cat $OUT/cfg4_ours.jsonl | cut -c1-400
 fi
 if [[ $ARMS == *ref* ]]; then
-  for sm in layer row; do
+  MODES="layer row"; [[ $ARMS == *ref-layer* ]] && MODES="layer"
+  for sm in $MODES; do
     C=$(clocks $OUT/cfg4_ref_${sm}_clocks.csv)
     CUDA_VISIBLE_DEVICES=$GPUS timeout 200 $REF/llama-batched-bench -m "$P4" -c 8192 -b 2048 -ub 512 -npp 16 -ntg 32 -npl 1,8,32 -ngl 99 -fa 1 -sm $sm --output-format jsonl \
       > $OUT/cfg4_ref_$sm.jsonl 2> $OUT/cfg4_ref_$sm.err
@@ -55,8 +59,10 @@ if [[ $ARMS == *ref* ]]; then
     grep -h '{' $OUT/cfg4_ref_$sm.jsonl $OUT/cfg4_ref_$sm.err | grep n_kv | cut -c1-300
   done
 fi
+fi
 
 # ---------------- config 5 ----------------
+if [[ $ONLY == *5* ]]; then
 P5=$(gen "$M5" Q4_K_M)
 VOC=32000
 wait_port() {  # until GET /health answers 200 (llama-server binds its port before the model is loaded)
@@ -85,7 +91,8 @@ if [[ $ARMS == *ours* ]]; then
   if wait_port 3105; then
     python tools/serve_bench.py --port 3105 --route /completion -c 1,4,16 --prompt-tokens 128 -n 64 --vocab $VOC --tag ours-completion -o $OUT/cfg5_ours_completion.json
     python tools/serve_bench.py --port 3105 --route /chat -c 1,4,16 --prompt-tokens 128 -n 64 --vocab $VOC --tag ours-chat -o $OUT/cfg5_ours_chat.json
-  else echo "cfg5 ours: server did not come up"; tail -5 $OUT/cfg5_ours_server.log; fi
+    grep -h "warm-up\|grid:" $OUT/cfg5_ours_server.log | head -3
+  else echo "cfg5 ours: server did not come up"; grep -v "Warn\|warn\|from_numpy" $OUT/cfg5_ours_server.log | tail -8 | cut -c1-300; fi
   kill -INT -- -$SRV 2>/dev/null; sleep 3; kill -KILL -- -$SRV 2>/dev/null; kill $C 2>/dev/null
 fi
 if [[ $ARMS == *ref* ]]; then
@@ -97,5 +104,6 @@ if [[ $ARMS == *ref* ]]; then
     python tools/serve_bench.py --port 3106 --route /completion -c 1,4,16 --prompt-tokens 128 -n 64 --vocab $VOC --tag ref-llama-server -o $OUT/cfg5_ref_completion.json
   else echo "cfg5 ref: llama-server did not come up"; tail -5 $OUT/cfg5_ref_server.log; fi
   kill -INT -- -$SRV 2>/dev/null; sleep 2; kill -KILL -- -$SRV 2>/dev/null; kill $C 2>/dev/null
+fi
 fi
 echo "configs done"
