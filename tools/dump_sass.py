@@ -30,12 +30,21 @@ HOT = [
     ("gemv_quant_q4_k_t1", r"gemv_quant_kernel<12, 1>"),
     ("attn_decode_d128_g4", r"attn_decode_kernel<128, 4>"),
     ("attn_prefill_d128", r"attn_prefill_kernel<128>"),
+    ("attn_prefill_tc_d128", r"attn_prefill_tc_kernel<128>"),
+    ("attn_prefill_tc_d64", r"attn_prefill_tc_kernel<64>"),
+    ("argmax_tp", r"argmax_tp_kernel"),
+    ("ar_consume", r"ar_consume_kernel"),
+    ("rs_norm_ag", r"rs_norm_ag_kernel"),
+    ("moe_route_ex", r"moe_route_ex_kernel"),
+    ("moe_plan", r"moe_plan_kernel"),
+    ("moe_combine", r"moe_combine_kernel"),
+    ("sample_dev", r"sample_dev_kernel"),
     ("rope_kv_f32", r"rope_kv_kernel<float, false>"),
     ("rope_kv_f32_bias_qknorm", r"rope_kv_kernel<float, true>"),
     ("rmsnorm", r"rmsnorm_kernel"),
     ("sample", r"sample_kernel"),
 ]
-KEY = ["UCGABAR_ARV", "UCGABAR_WAIT", "MAPA", "MEMBAR", "ACQBULK", "UBLKPF", "UTCHMMA", "UTCQMMA", "LDTM", "STTM", "UTMALDG", "UTMASTG", "UTCBAR", "SYNCS", "HMMA", "LDGSTS", "LDSM", "FFMA", "HFMA2", "LDG", "STG", "RED", "ATOM"]
+KEY = ["STMC", "LDGMC", "REDMC", "UCGABAR_ARV", "UCGABAR_WAIT", "MAPA", "MEMBAR", "ACQBULK", "UBLKPF", "UTCHMMA", "UTCQMMA", "LDTM", "STTM", "UTMALDG", "UTMASTG", "UTCBAR", "SYNCS", "HMMA", "LDGSTS", "LDSM", "FFMA", "HFMA2", "LDG", "STG", "RED", "ATOM"]
 
 
 def main():
@@ -68,7 +77,7 @@ def main():
     with open(os.path.join(OUT, "SUMMARY.md"), "w") as f:
         f.write("# SASS evidence (cuobjdump -sass libdlp_b200.so, sm_100a)\n\n"
                 "`UTCHMMA` = tcgen05.mma, `LDTM` = tcgen05.ld, `UTMALDG` = TMA load, `UTCBAR` = tcgen05.commit, `SYNCS` = mbarrier, "
-                "`HMMA` = legacy mma.sync (flash-prefill only).\n\n| listing | kernel | instrs | key mnemonics |\n|---|---|---:|---|\n")
+                "`HMMA` = legacy mma.sync (only in the A/B prefill-attention kernel `attn_prefill_d128`), `STTM` = tcgen05.st, `multimem.st` lowers to an ordinary `STG.E.64.STRONG.SYS` whose address is the NVLS multicast alias (ptxas emits `LDGMC` / `REDG` only for `multimem.ld_reduce` / `multimem.red`, which this code does not use): the fused all-reduce stores are the `STG...STRONG.SYS` of gemv_dense_v3 / gemv_quant_v3 / argmax_tp, the PTX is in `csrc/tpcomm.cuh`, `UCGABAR` = cluster barrier, `MAPA` = DSMEM address mapping.\n\n| listing | kernel | instrs | key mnemonics |\n|---|---|---:|---|\n")
         for stem, dem, n, ops in rows:
             f.write(f"| [{stem}.sass]({stem}.sass) | `{dem[:90]}` | {n} | {', '.join(f'{k} {v}' for k, v in ops.items())} |\n")
     print(open(os.path.join(OUT, "SUMMARY.md")).read())
