@@ -148,7 +148,7 @@ class LlamaEngine:
         self.samp = torch.zeros(max_seqs, ops.SAMPLE_REC_WORDS, dtype=i32, device=dev)
         self._samp_host: dict[int, tuple] = {}      # what each record currently holds
         self._seq_sampling: dict[int, tuple] = {}   # per-sequence overrides of self.sampling (set_seq_sampling)
-        self.max_graphs = int(os.environ.get("DLP_MAX_GRAPHS", "24"))
+        self.max_graphs = int(os.environ.get("DLP_MAX_GRAPHS", str(max(24, 4 * max_seqs + 8))))   # (batch sizes x attention variants x greedy)
         v0, v1 = weights.vocab_range
         self.logits = torch.zeros(max(max_seqs, 1), v1 - v0, dtype=f32, device=dev) if last_stage else None
         if last_stage and self.comm.tp_size > 1 and hasattr(self.comm, "reserve_logits") and (v1 - v0) != cfg.vocab_size:
@@ -364,8 +364,9 @@ class LlamaEngine:
         """Top-k routed experts (softmax over all experts, top-k, renormalise: llama-graph.cpp:1039-1139)."""
         cfg, comm = self.cfg, self.comm
         h = self.h[:T]
-        if (T <= 4 and lw.e_gate_s is not None and cfg.n_expert <= 32 and cfg.n_embd % 256 == 0 and comm.tp_size == 1
-                and lw.router_w.N % 2 == 0 and cfg.moe_norm_topk and not cfg.n_ff_shared):
+        if (T <= 4 and lw.e_gate_s is not None and cfg.n_expert <= 32 and cfg.n_embd % 256 == 0 and self.F % 256 == 0
+                and lw.router_w.N % 2 == 0 and cfg.moe_norm_topk and not cfg.n_ff_shared and self.device.type == "cuda"
+                and os.environ.get("DLP_MOE_GEMV", "1") == "1"):
             return self._moe_device(lw, T)
         if xn is None:
             xn = ops.rmsnorm(h, lw.ffn_norm, cfg.rms_eps, out=self.xn[:T])
@@ -449,6 +450,13 @@ class LlamaEngine:
                                 act=torch.zeros(4 * k, F, dtype=torch.float16, device=dev))
         b = self.moe_buf
         h = self.h[:T]
+        # Under tensor parallelism every expert's n_ff is sharded: the down mat-vecs accumulate this rank's partial sums into a
+        # zeroed delta, which takes one all-reduce per layer (the bandwidth-bound mat-vec kernels use every SM for a single token,
+        # where the grouped GEMM has two token tiles to offer: config 5 ran 0.63x the reference at one request through that path)
+        tp = self.comm.tp_size > 1
+        tgt = self.delta[:T] if tp else h
+        if tp:
+            tgt.zero_()
         for t in range(T):   # router per token (T <= 4): the mat-vec path supports T in {1,2,4}, the router is tiny
             ops.linear(lw.router_w, h[t:t + 1], "f32", norm_w=lw.ffn_norm, eps=cfg.rms_eps, out=b["logits"][t:t + 1])
         ops.moe_route(b["logits"][:T], k, b["ids"][:T * k], b["w"][:T * k])
@@ -459,8 +467,10 @@ class LlamaEngine:
                              norm_w=lw.ffn_norm, eps=cfg.rms_eps)
             for j in range(k):   # all gate/up mat-vecs read h[t] before any down mat-vec updates it
                 job = t * k + j
-                ops.gemv_moe(lw.e_down_s, b["act"][job:job + 1], h[t:t + 1], "add", b["ids"][job:job + 1], self.E,
+                ops.gemv_moe(lw.e_down_s, b["act"][job:job + 1], tgt[t:t + 1], "add", b["ids"][job:job + 1], self.E,
                              out_scale=b["w"][job:job + 1])
+        if tp:
+            h.add_(self.comm.allreduce_delta(tgt, -1, 1))
 
     # ---- attention flavours ---------------------------------------------------------------------
     def _attn_decode(self, il, q, T):

@@ -120,7 +120,7 @@ class DeviceWeight:
             return cls(GGMLType.F16, N, K, [w])
         if K % 256:
             raise ValueError(f"K={K} must be a multiple of 256 for the device kernels")
-        buf = torch.from_numpy(raw).to(device, non_blocking=False)
+        buf = _upload(raw, device)
         if t in (GGMLType.F16, GGMLType.BF16):
             return cls(t, N, K, [buf.view(torch.float16 if t == GGMLType.F16 else torch.bfloat16).view(N, K)])
         if t in (GGMLType.Q4_K, GGMLType.Q5_K):
@@ -146,6 +146,62 @@ class DeviceWeight:
         N, K = w.shape
         raw = quantize(w.detach().float().cpu().numpy(), ggml_type)
         return cls.from_raw(raw, ggml_type, (N, K), device or w.device)
+
+
+class _Stager:
+    """Pinned staging ring for weight uploads: 4 x 64 MiB page-locked buffers with one CUDA event each.  The (read-only, mmap-backed)
+    GGUF bytes are copied into a free buffer on the host while the previous buffers are still in flight to the device, so file
+    reads and H2D DMA overlap.  Parity: `llama_model_loader::load_all_data` (llama.cpp/src/llama-model-loader.cpp:970-1172: four
+    64 MiB pinned staging buffers + events around `ggml_backend_tensor_set_async`)."""
+    N_BUF, BYTES = 4, 64 << 20
+
+    def __init__(self):
+        self.bufs = [torch.empty(self.BYTES, dtype=torch.uint8).pin_memory() for _ in range(self.N_BUF)]
+        self.views = [b.numpy() for b in self.bufs]
+        self.events = [torch.cuda.Event() for _ in range(self.N_BUF)]
+        self.used = [False] * self.N_BUF
+        self.i = 0
+
+    def upload(self, raw: np.ndarray, device) -> torch.Tensor:
+        flat = raw.reshape(-1).view(np.uint8)
+        n = flat.shape[0]
+        out = torch.empty(n, dtype=torch.uint8, device=device)
+        for off in range(0, n, self.BYTES):
+            m = min(self.BYTES, n - off)
+            k = self.i
+            self.i = (self.i + 1) % self.N_BUF
+            if self.used[k]:
+                self.events[k].synchronize()          # the DMA that last read this buffer has finished
+            np.copyto(self.views[k][:m], flat[off:off + m])
+            out[off:off + m].copy_(self.bufs[k][:m], non_blocking=True)
+            self.events[k].record()
+            self.used[k] = True
+        return out.view(raw.shape)
+
+
+_STAGER: _Stager | None = None
+
+
+def _upload(raw: np.ndarray, device) -> torch.Tensor:
+    """Host bytes -> device tensor of the same shape (uint8), through the pinned staging ring on CUDA devices."""
+    global _STAGER
+    if torch.device(device).type != "cuda":
+        return torch.from_numpy(np.array(raw, copy=True)).to(device)
+    with torch.cuda.device(device):
+        if _STAGER is None:
+            try:
+                _STAGER = _Stager()
+            except RuntimeError:                      # no pinned memory to be had: plain synchronous copy
+                return torch.from_numpy(np.array(raw, copy=True)).to(device)
+        return _STAGER.upload(raw, device)
+
+
+def release_staging():
+    """Free the pinned staging buffers (call after loading when host memory matters)."""
+    global _STAGER
+    if _STAGER is not None:
+        torch.cuda.synchronize()
+        _STAGER = None
 
 
 def stack_rows(weights: list[DeviceWeight]) -> DeviceWeight:
