@@ -39,6 +39,28 @@ def env() -> dict:
     return e
 
 
+def cpu_env(scratch: str) -> dict:
+    """Environment for running the reference's ggml-cpu back-end (`-ngl 0`) on a machine without an NVIDIA driver.
+
+    The binaries are the CUDA build, so the loader wants `libcuda.so.1`; where the driver library is absent the toolkit's link
+    stub stands in (its `cuInit` fails, ggml reports "no CUDA devices" and every tensor stays on the CPU back-end).
+    """
+    import ctypes
+    e = env()
+    try:
+        ctypes.CDLL("libcuda.so.1")
+    except OSError:
+        stub = os.path.join(os.environ.get("CUDA_HOME", "/usr/local/cuda"), "lib64", "stubs", "libcuda.so")
+        if os.path.exists(stub):
+            os.makedirs(scratch, exist_ok=True)
+            link = os.path.join(scratch, "libcuda.so.1")
+            if not os.path.exists(link):
+                os.symlink(stub, link)
+            e["LD_LIBRARY_PATH"] = e["LD_LIBRARY_PATH"].rstrip(":") + ":" + scratch
+    e["CUDA_VISIBLE_DEVICES"] = ""
+    return e
+
+
 def ensure(allow_build: bool = True, build_timeout_s: float | None = None, log=lambda s: None) -> str | None:
     """Returns None when the reference is in place, else a one-line reason."""
     if have():
