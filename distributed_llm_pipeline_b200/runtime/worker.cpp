@@ -36,6 +36,8 @@
 #include <string>
 #include <vector>
 
+#include <omp.h>
+
 namespace {
 
 constexpr uint32_t PROTO_VERSION = 1;
@@ -48,11 +50,26 @@ using namespace dlp_gguf;
 // ---- Q8_0 fast path: int8 activations (one fp32 scale per 32 values) x int8 weights with AVX2 integer dot products.
 // Same numerics class as the reference's CPU vec-dot for Q8_0 (q8_0 x q8_0, ggml-cpu/quants.c); ~4x the throughput of
 // decoding to fp32 first, which matters because the CPU configuration is the only one where compute, not HBM, limits us.
-struct QAct { std::vector<int8_t> q; std::vector<float> d; };
+struct QAct { std::vector<int8_t> q; std::vector<float> d, c; };   // c[t][b] = -128 * d * sum(q): offset term of the VNNI path
+
+// DLP_WORKER_PROF=1: seconds per phase of every RUN on stderr (where a prefill goes: mat-muls, attention, the rest)
+struct Prof {
+    bool on = getenv("DLP_WORKER_PROF") != nullptr;
+    double t0 = 0, acc[6] = {0, 0, 0, 0, 0, 0};
+    void start() { if (on) t0 = omp_get_wtime(); }
+    void lap(int i) { if (on) { const double t = omp_get_wtime(); acc[i] += t - t0; t0 = t; } }
+    void report(int T) {
+        if (!on) return;
+        fprintf(stderr, "prof T=%d: matmul %.1f ms, attention %.1f ms, norm %.1f ms, rope+kv %.1f ms, act %.1f ms, head %.1f ms\n", T,
+                acc[0] * 1e3, acc[1] * 1e3, acc[2] * 1e3, acc[3] * 1e3, acc[4] * 1e3, acc[5] * 1e3);
+        for (double& a : acc) a = 0;
+    }
+};
 
 void quantize_act(const float* x, int T, uint64_t K, QAct& a) {
     a.q.resize((size_t)T * K);
     a.d.resize((size_t)T * (K / 32));
+    a.c.resize((size_t)T * (K / 32));
 #pragma omp parallel for schedule(static)
     for (int64_t b = 0; b < (int64_t)(T * (K / 32)); ++b) {
         const float* p = x + (size_t)b * 32;
@@ -60,7 +77,9 @@ void quantize_act(const float* x, int T, uint64_t K, QAct& a) {
         for (int i = 0; i < 32; ++i) amax = std::max(amax, std::fabs(p[i]));
         const float d = amax / 127.f, inv = amax > 0 ? 127.f / amax : 0.f;
         a.d[b] = d;
-        for (int i = 0; i < 32; ++i) a.q[(size_t)b * 32 + i] = (int8_t)std::lrintf(p[i] * inv);
+        int sum = 0;
+        for (int i = 0; i < 32; ++i) { const int8_t v = (int8_t)std::lrintf(p[i] * inv); a.q[(size_t)b * 32 + i] = v; sum += v; }
+        a.c[b] = -128.f * d * (float)sum;
     }
 }
 
@@ -89,48 +108,194 @@ inline float hsum256(__m256 v) {
     return _mm_cvtss_f32(s);
 }
 
+// R weight rows x 4 tokens per pass over K: each weight block is decoded (|w|, sign source, scale) once for four tokens and
+// each activation block is loaded once for R rows.
+template <int R>
+inline void tile_q8_0(const uint8_t* wr, size_t rb, const int8_t* xq, const float* xd, uint64_t K, uint64_t nblk, float* out /*[R][4]*/) {
+    const __m256i ones = _mm256_set1_epi16(1);
+    __m256 acc[R][4];
+    for (int r = 0; r < R; ++r) for (int j = 0; j < 4; ++j) acc[r][j] = _mm256_setzero_ps();
+    for (uint64_t b = 0; b < nblk; ++b) {
+        __m256i wv[R], aw[R];
+        float dw[R];
+        for (int r = 0; r < R; ++r) {
+            const uint8_t* p = wr + r * rb + b * 34;
+            uint16_t dh; memcpy(&dh, p, 2);
+            dw[r] = f16(dh);
+            wv[r] = _mm256_loadu_si256((const __m256i*)(p + 2));
+            aw[r] = _mm256_sign_epi8(wv[r], wv[r]);
+        }
+#pragma GCC unroll 4
+        for (int j = 0; j < 4; ++j) {
+            const __m256i xv = _mm256_loadu_si256((const __m256i*)(xq + (size_t)j * K + b * 32));
+            const float dx = xd[(size_t)j * nblk + b];
+            for (int r = 0; r < R; ++r) {
+                const __m256i p32 = _mm256_madd_epi16(_mm256_maddubs_epi16(aw[r], _mm256_sign_epi8(xv, wv[r])), ones);
+                acc[r][j] = _mm256_fmadd_ps(_mm256_cvtepi32_ps(p32), _mm256_set1_ps(dw[r] * dx), acc[r][j]);
+            }
+        }
+    }
+    for (int r = 0; r < R; ++r) for (int j = 0; j < 4; ++j) out[r * 4 + j] = hsum256(acc[r][j]);
+}
+
+// Cache blocking for prefill: a panel of weight rows (L2-resident) is swept by groups of four tokens whose int8 activations
+// (4 x K bytes) stay in L1 across the panel, instead of re-streaming the whole [T][K] activation matrix for every weight row.
 void matmul_q8_0(const Tensor& w, const QAct& a, int T, float* y, bool accumulate) {
     const uint64_t K = w.cols(), N = w.rows(), nblk = K / 32;
     const size_t rb = row_bytes(w.type, K);
-    const __m256i ones = _mm256_set1_epi16(1);
-#pragma omp parallel for schedule(static)
-    for (int64_t n = 0; n < (int64_t)N; ++n) {
-        const uint8_t* wr = w.data + n * rb;
+    constexpr int64_t PANEL = 32;
+    const int64_t n_panels = ((int64_t)N + PANEL - 1) / PANEL;
+#pragma omp parallel for schedule(dynamic, 1)
+    for (int64_t pi = 0; pi < n_panels; ++pi) {
+        const int64_t n0 = pi * PANEL, n1 = std::min<int64_t>(N, n0 + PANEL);
         int t = 0;
-        for (; t + 4 <= T; t += 4) {   // register blocking: one pass over the weight row feeds four tokens
-            __m256 acc[4] = {_mm256_setzero_ps(), _mm256_setzero_ps(), _mm256_setzero_ps(), _mm256_setzero_ps()};
-            for (uint64_t b = 0; b < nblk; ++b) {
-                const uint8_t* p = wr + b * 34;
-                uint16_t dh; memcpy(&dh, p, 2);
-                const float dw = f16(dh);
-                const __m256i wv = _mm256_loadu_si256((const __m256i*)(p + 2));
-                const __m256i aw = _mm256_sign_epi8(wv, wv);
-#pragma GCC unroll 4
+        for (; t + 4 <= T; t += 4) {
+            const int8_t* xq = a.q.data() + (size_t)t * K;
+            const float* xd = a.d.data() + (size_t)t * nblk;
+            float out[8];
+            int64_t n = n0;
+            for (; n + 2 <= n1; n += 2) {
+                tile_q8_0<2>(w.data + n * rb, rb, xq, xd, K, nblk, out);
+                for (int r = 0; r < 2; ++r)
+                    for (int j = 0; j < 4; ++j) {
+                        float& d = y[(size_t)(t + j) * N + n + r];
+                        d = accumulate ? d + out[r * 4 + j] : out[r * 4 + j];
+                    }
+            }
+            for (; n < n1; ++n) {
+                tile_q8_0<1>(w.data + n * rb, rb, xq, xd, K, nblk, out);
                 for (int j = 0; j < 4; ++j) {
-                    const __m256i xv = _mm256_loadu_si256((const __m256i*)(a.q.data() + (size_t)(t + j) * K + b * 32));
-                    const __m256i p32 = _mm256_madd_epi16(_mm256_maddubs_epi16(aw, _mm256_sign_epi8(xv, wv)), ones);
-                    acc[j] = _mm256_fmadd_ps(_mm256_cvtepi32_ps(p32), _mm256_set1_ps(dw * a.d[(size_t)(t + j) * nblk + b]), acc[j]);
+                    float& d = y[(size_t)(t + j) * N + n];
+                    d = accumulate ? d + out[j] : out[j];
                 }
             }
-            for (int j = 0; j < 4; ++j) {
-                const float v = hsum256(acc[j]);
-                if (accumulate) y[(size_t)(t + j) * N + n] += v; else y[(size_t)(t + j) * N + n] = v;
+        }
+        for (; t < T; ++t)
+            for (int64_t n = n0; n < n1; ++n) {
+                const float v = dot_q8_0_row(w.data + n * rb, a.q.data() + (size_t)t * K, a.d.data() + (size_t)t * nblk, nblk);
+                if (accumulate) y[(size_t)t * N + n] += v; else y[(size_t)t * N + n] = v;
+            }
+    }
+}
+
+// ---- AVX-512 VNNI variant (chosen at run time).  vpdpbusd multiplies unsigned by signed bytes into int32 lanes without the
+// int16 saturation of vpmaddubsw, so the weights go in as w + 128 (one xor per weight block, shared by the token group) and the
+// offset 128 * sum(x) leaves again through a per-(token, block) term prepared by quantize_act.  One 512-bit operation covers two
+// 32-value blocks; their two scales sit in the low and high halves of the scale vector.  Per 64 multiply-adds: vpdpbusd, convert,
+// scale product, fma - against six AVX2 operations per 32.
+#define DLP_VNNI __attribute__((target("avx512f,avx512bw,avx512vl,avx512dq,avx512vnni,avx2,fma,f16c")))
+
+DLP_VNNI inline __m512 pair_scale(const float* p, __m512i half_sel) {   // (p[0] x 8 | p[1] x 8)
+    double two; memcpy(&two, p, 8);
+    return _mm512_permutexvar_ps(half_sel, _mm512_castpd_ps(_mm512_set1_pd(two)));
+}
+
+template <int R>
+DLP_VNNI inline void tile_q8_0_vnni(const uint8_t* wr, size_t rb, const float* dws, const int8_t* xq, const float* xd, const float* xc,
+                                    uint64_t K, uint64_t nblk, float* out /*[R][4]*/) {
+    const __m512i half_sel = _mm512_set_epi32(1, 1, 1, 1, 1, 1, 1, 1, 0, 0, 0, 0, 0, 0, 0, 0);
+    const __m512i bias = _mm512_set1_epi8((char)0x80);
+    __m512 acc[R][4];
+    for (int r = 0; r < R; ++r) for (int j = 0; j < 4; ++j) acc[r][j] = _mm512_setzero_ps();
+    for (uint64_t b = 0; b + 2 <= nblk; b += 2) {
+        __m512i wu[R];
+        __m512 dwv[R];
+        for (int r = 0; r < R; ++r) {
+            const uint8_t* p = wr + r * rb + b * 34;
+            const __m256i lo = _mm256_loadu_si256((const __m256i*)(p + 2)), hi = _mm256_loadu_si256((const __m256i*)(p + 36));
+            wu[r] = _mm512_xor_si512(_mm512_inserti64x4(_mm512_castsi256_si512(lo), hi, 1), bias);
+            dwv[r] = pair_scale(dws + r * nblk + b, half_sel);
+        }
+#pragma GCC unroll 4
+        for (int j = 0; j < 4; ++j) {
+            const __m512i xv = _mm512_loadu_si512((const void*)(xq + (size_t)j * K + b * 32));
+            const __m512 dxv = pair_scale(xd + (size_t)j * nblk + b, half_sel);
+            for (int r = 0; r < R; ++r) {
+                const __m512i dp = _mm512_dpbusd_epi32(_mm512_setzero_si512(), wu[r], xv);
+                acc[r][j] = _mm512_fmadd_ps(_mm512_cvtepi32_ps(dp), _mm512_mul_ps(dwv[r], dxv), acc[r][j]);
             }
         }
-        for (; t < T; ++t) {
-            const float v = dot_q8_0_row(wr, a.q.data() + (size_t)t * K, a.d.data() + (size_t)t * nblk, nblk);
-            if (accumulate) y[(size_t)t * N + n] += v; else y[(size_t)t * N + n] = v;
+    }
+    for (int r = 0; r < R; ++r)
+        for (int j = 0; j < 4; ++j) {
+            const float* dw = dws + r * nblk;
+            const float* c = xc + (size_t)j * nblk;
+            __m512 corr = _mm512_setzero_ps();
+            uint64_t b = 0;
+            for (; b + 16 <= nblk; b += 16) corr = _mm512_fmadd_ps(_mm512_loadu_ps(dw + b), _mm512_loadu_ps(c + b), corr);
+            float tail = 0.f;
+            for (; b < nblk; ++b) tail += dw[b] * c[b];
+            out[r * 4 + j] = _mm512_reduce_add_ps(_mm512_add_ps(acc[r][j], corr)) + tail;
+        }
+}
+
+DLP_VNNI void matmul_q8_0_vnni(const Tensor& w, const QAct& a, int T, float* y, bool accumulate) {
+    const uint64_t K = w.cols(), N = w.rows(), nblk = K / 32;
+    const size_t rb = row_bytes(w.type, K);
+    constexpr int64_t PANEL = 32;
+    const int64_t n_panels = ((int64_t)N + PANEL - 1) / PANEL;
+#pragma omp parallel
+    {
+        std::vector<float> dws((size_t)PANEL * nblk);
+#pragma omp for schedule(dynamic, 1)
+        for (int64_t pi = 0; pi < n_panels; ++pi) {
+            const int64_t n0 = pi * PANEL, n1 = std::min<int64_t>(N, n0 + PANEL);
+            int t = 0;
+            if (T >= 4)      // the panel's block scales as fp32, once for all token groups
+                for (int64_t n = n0; n < n1; ++n)
+                    for (uint64_t b = 0; b < nblk; ++b) { uint16_t dh; memcpy(&dh, w.data + n * rb + b * 34, 2); dws[(size_t)(n - n0) * nblk + b] = f16(dh); }
+            for (; t + 4 <= T; t += 4) {
+                const int8_t* xq = a.q.data() + (size_t)t * K;
+                const float* xd = a.d.data() + (size_t)t * nblk;
+                const float* xc = a.c.data() + (size_t)t * nblk;
+                float out[16];
+                int64_t n = n0;
+                for (; n + 4 <= n1; n += 4) {
+                    tile_q8_0_vnni<4>(w.data + n * rb, rb, dws.data() + (size_t)(n - n0) * nblk, xq, xd, xc, K, nblk, out);
+                    for (int r = 0; r < 4; ++r)
+                        for (int j = 0; j < 4; ++j) {
+                            float& d = y[(size_t)(t + j) * N + n + r];
+                            d = accumulate ? d + out[r * 4 + j] : out[r * 4 + j];
+                        }
+                }
+                for (; n < n1; ++n) {
+                    tile_q8_0_vnni<1>(w.data + n * rb, rb, dws.data() + (size_t)(n - n0) * nblk, xq, xd, xc, K, nblk, out);
+                    for (int j = 0; j < 4; ++j) {
+                        float& d = y[(size_t)(t + j) * N + n];
+                        d = accumulate ? d + out[j] : out[j];
+                    }
+                }
+            }
+            for (; t < T; ++t)
+                for (int64_t n = n0; n < n1; ++n) {
+                    const float v = dot_q8_0_row(w.data + n * rb, a.q.data() + (size_t)t * K, a.d.data() + (size_t)t * nblk, nblk);
+                    if (accumulate) y[(size_t)t * N + n] += v; else y[(size_t)t * N + n] = v;
+                }
         }
     }
 }
 
+bool have_vnni() {
+    static const bool ok = __builtin_cpu_supports("avx512vnni") && __builtin_cpu_supports("avx512bw") && __builtin_cpu_supports("avx512vl") &&
+                           __builtin_cpu_supports("avx512dq") && getenv("DLP_WORKER_NO_VNNI") == nullptr;
+    return ok;
+}
+
+// An activation matrix used by several mat-muls (q / k / v, gate / up): its int8 form is made once, on first need.
+struct Act {
+    const float* x; int T; uint64_t K; QAct qa; bool have = false;
+    Act(const float* x_, int T_, uint64_t K_) : x(x_), T(T_), K(K_) {}
+    const QAct& q8() { if (!have) { quantize_act(x, T, K, qa); have = true; } return qa; }
+};
+
 // y[T][N] = x[T][K] . W[N][K]^T     (W decoded row by row, shared across the T tokens)
-void matmul(const Tensor& w, const float* x, int T, float* y, bool accumulate = false) {
+void matmul(const Tensor& w, Act& act, float* y, bool accumulate = false) {
     const uint64_t K = w.cols(), N = w.rows();
+    const float* x = act.x;
+    const int T = act.T;
     if (w.type == T_Q8_0 && K % 32 == 0) {
-        QAct a;
-        quantize_act(x, T, K, a);
-        matmul_q8_0(w, a, T, y, accumulate);
+        if (T >= 4 && K % 64 == 0 && have_vnni()) matmul_q8_0_vnni(w, act.q8(), T, y, accumulate);
+        else matmul_q8_0(w, act.q8(), T, y, accumulate);
         return;
     }
     const size_t rb = row_bytes(w.type, K);
@@ -151,6 +316,7 @@ void matmul(const Tensor& w, const float* x, int T, float* y, bool accumulate = 
 }
 
 void rmsnorm(const float* x, const float* w, float eps, int T, int E, float* out) {
+#pragma omp parallel for schedule(static) if (T >= 8)
     for (int t = 0; t < T; ++t) {
         const float* r = x + (size_t)t * E;
         double ss = 0;
@@ -173,6 +339,7 @@ struct Stage {
     bool first = false, last = false;
     std::vector<float> inv_freq;
     std::map<uint32_t, SeqCache> seqs;
+    Prof prof;
     int max_seqs = 64;           // --max-seqs: cap on live sequences (each holds an n_ctx KV cache)
 
     void load(const std::string& path, int a, int b, int n_ctx) {
@@ -213,16 +380,43 @@ struct Stage {
         return c;
     }
 
-    void rope(float* x, int n_heads, int pos) const {
-        const int D = hp.head_dim;
+    void rope(float* x, int n_heads, const float* cs, const float* sn) const {
+        const int D = hp.head_dim, R2 = hp.n_rot / 2;
         for (int h = 0; h < n_heads; ++h)
-            for (int i = 0; i < hp.n_rot / 2; ++i) {
-                const float a = pos * inv_freq[i], c = std::cos(a), s = std::sin(a);
+            for (int i = 0; i < R2; ++i) {
                 float* p0 = x + (size_t)h * D + (hp.neox ? i : 2 * i);
-                float* p1 = hp.neox ? p0 + hp.n_rot / 2 : p0 + 1;
+                float* p1 = hp.neox ? p0 + R2 : p0 + 1;
                 const float x0 = *p0, x1 = *p1;
-                *p0 = x0 * c - x1 * s; *p1 = x0 * s + x1 * c;
+                *p0 = x0 * cs[i] - x1 * sn[i]; *p1 = x0 * sn[i] + x1 * cs[i];
             }
+    }
+
+    // causal attention of T new queries (positions pos0 ..) over the fp32 cache of one layer; one (token, head) per task
+    void attention(const float* q, const float* kc, const float* vc, float* att, int T, int pos0, float scale) const {
+        const int D = hp.head_dim, Hq = hp.n_head, Hkv = hp.n_head_kv, qd = Hq * D, kvd = Hkv * D, gqa = Hq / Hkv;
+#pragma omp parallel
+        {
+            std::vector<float> s((size_t)pos0 + T);
+#pragma omp for collapse(2) schedule(dynamic, 8)
+            for (int t = 0; t < T; ++t)
+                for (int hq = 0; hq < Hq; ++hq) {
+                    const int n_keys = pos0 + t + 1, kvh = hq / gqa;
+                    const float* qv = q + (size_t)t * qd + (size_t)hq * D;
+                    float mx = -INFINITY;
+                    for (int j = 0; j < n_keys; ++j) { s[j] = scale * dot(qv, kc + (size_t)j * kvd + (size_t)kvh * D, D); mx = std::max(mx, s[j]); }
+                    float sum = 0;
+                    for (int j = 0; j < n_keys; ++j) { s[j] = std::exp(s[j] - mx); sum += s[j]; }
+                    float* o = att + (size_t)t * qd + (size_t)hq * D;
+                    for (int d = 0; d < D; ++d) o[d] = 0;
+                    const float inv = 1.0f / sum;
+                    for (int j = 0; j < n_keys; ++j) {
+                        const float w = s[j] * inv;
+                        const float* vv = vc + (size_t)j * kvd + (size_t)kvh * D;
+#pragma omp simd
+                        for (int d = 0; d < D; ++d) o[d] += w * vv[d];
+                    }
+                }
+        }
     }
 
     // in: token ids (first stage) or hidden [T][E]; out: hidden [T][E] or logits ([1|T][vocab]) on the last stage
@@ -251,19 +445,31 @@ struct Stage {
         std::vector<float> xn((size_t)T * E), q((size_t)T * qd), k((size_t)T * kvd), v((size_t)T * kvd), att((size_t)T * qd),
             gate((size_t)T * F), up((size_t)T * F);
         const float scale = 1.0f / std::sqrt((float)D);
+        // rotation angles depend on (position, pair) only: one table per call instead of cos/sin per layer and head
+        const int R2 = hp.n_rot / 2;
+        std::vector<float> rc((size_t)T * R2), rs((size_t)T * R2);
+#pragma omp parallel for schedule(static) if (T >= 8)
+        for (int t = 0; t < T; ++t)
+            for (int i = 0; i < R2; ++i) { const float a = (pos0 + t) * inv_freq[i]; rc[(size_t)t * R2 + i] = std::cos(a); rs[(size_t)t * R2 + i] = std::sin(a); }
+        prof.start();
         for (int il = l0; il < l1; ++il) {
             const std::string p = "blk." + std::to_string(il) + ".";
             rmsnorm(h.data(), (const float*)g.get(p + "attn_norm.weight").data, hp.eps, T, E, xn.data());
-            if (hp.fused_qkv) {
-                const Tensor& w = g.get(p + "attn_qkv.weight");
-                matmul(slice_rows(w, 0, qd), xn.data(), T, q.data());
-                matmul(slice_rows(w, qd, qd + kvd), xn.data(), T, k.data());
-                matmul(slice_rows(w, qd + kvd, qd + 2 * kvd), xn.data(), T, v.data());
-            } else {
-                matmul(g.get(p + "attn_q.weight"), xn.data(), T, q.data());
-                matmul(g.get(p + "attn_k.weight"), xn.data(), T, k.data());
-                matmul(g.get(p + "attn_v.weight"), xn.data(), T, v.data());
+            prof.lap(2);
+            {
+                Act a(xn.data(), T, E);
+                if (hp.fused_qkv) {
+                    const Tensor& w = g.get(p + "attn_qkv.weight");
+                    matmul(slice_rows(w, 0, qd), a, q.data());
+                    matmul(slice_rows(w, qd, qd + kvd), a, k.data());
+                    matmul(slice_rows(w, qd + kvd, qd + 2 * kvd), a, v.data());
+                } else {
+                    matmul(g.get(p + "attn_q.weight"), a, q.data());
+                    matmul(g.get(p + "attn_k.weight"), a, k.data());
+                    matmul(g.get(p + "attn_v.weight"), a, v.data());
+                }
             }
+            prof.lap(0);
             if (hp.qkv_bias) {
                 const float* bq = (const float*)g.get(p + "attn_q.bias").data;
                 const float* bk = (const float*)g.get(p + "attn_k.bias").data;
@@ -284,47 +490,56 @@ struct Stage {
             }
             std::vector<float>& kc = c.k[il - l0];
             std::vector<float>& vc = c.v[il - l0];
+#pragma omp parallel for schedule(static) if (T >= 8)
             for (int t = 0; t < T; ++t) {
-                rope(q.data() + (size_t)t * qd, Hq, pos0 + t);
-                rope(k.data() + (size_t)t * kvd, Hkv, pos0 + t);
+                rope(q.data() + (size_t)t * qd, Hq, rc.data() + (size_t)t * R2, rs.data() + (size_t)t * R2);
+                rope(k.data() + (size_t)t * kvd, Hkv, rc.data() + (size_t)t * R2, rs.data() + (size_t)t * R2);
                 memcpy(kc.data() + (size_t)(pos0 + t) * kvd, k.data() + (size_t)t * kvd, kvd * 4);
                 memcpy(vc.data() + (size_t)(pos0 + t) * kvd, v.data() + (size_t)t * kvd, kvd * 4);
             }
-#pragma omp parallel for collapse(2) schedule(static)
-            for (int t = 0; t < T; ++t)
-                for (int hq = 0; hq < Hq; ++hq) {
-                    const int n_keys = pos0 + t + 1, kvh = hq / gqa;
-                    const float* qv = q.data() + (size_t)t * qd + (size_t)hq * D;
-                    std::vector<float> s(n_keys);
-                    float mx = -INFINITY;
-                    for (int j = 0; j < n_keys; ++j) { s[j] = scale * dot(qv, kc.data() + (size_t)j * kvd + (size_t)kvh * D, D); mx = std::max(mx, s[j]); }
-                    float sum = 0;
-                    for (int j = 0; j < n_keys; ++j) { s[j] = std::exp(s[j] - mx); sum += s[j]; }
-                    float* o = att.data() + (size_t)t * qd + (size_t)hq * D;
-                    for (int d = 0; d < D; ++d) o[d] = 0;
-                    for (int j = 0; j < n_keys; ++j) { const float w = s[j] / sum; const float* vv = vc.data() + (size_t)j * kvd + (size_t)kvh * D; for (int d = 0; d < D; ++d) o[d] += w * vv[d]; }
-                }
-            matmul(g.get(p + "attn_output.weight"), att.data(), T, h.data(), true);
-            rmsnorm(h.data(), (const float*)g.get(p + "ffn_norm.weight").data, hp.eps, T, E, xn.data());
-            if (hp.fused_qkv) {   // phi3: ffn_up = [gate | up]
-                const Tensor& w = g.get(p + "ffn_up.weight");
-                matmul(slice_rows(w, 0, F), xn.data(), T, gate.data());
-                matmul(slice_rows(w, F, 2 * (uint64_t)F), xn.data(), T, up.data());
-            } else {
-                matmul(g.get(p + "ffn_gate.weight"), xn.data(), T, gate.data());
-                matmul(g.get(p + "ffn_up.weight"), xn.data(), T, up.data());
+            prof.lap(3);
+            attention(q.data(), kc.data(), vc.data(), att.data(), T, pos0, scale);
+            prof.lap(1);
+            {
+                Act a(att.data(), T, qd);
+                matmul(g.get(p + "attn_output.weight"), a, h.data(), true);
             }
-            for (size_t i = 0; i < (size_t)T * F; ++i) gate[i] = gate[i] / (1.0f + std::exp(-gate[i])) * up[i];
-            matmul(g.get(p + "ffn_down.weight"), gate.data(), T, h.data(), true);
+            prof.lap(0);
+            rmsnorm(h.data(), (const float*)g.get(p + "ffn_norm.weight").data, hp.eps, T, E, xn.data());
+            prof.lap(2);
+            {
+                Act a(xn.data(), T, E);
+                if (hp.fused_qkv) {   // phi3: ffn_up = [gate | up]
+                    const Tensor& w = g.get(p + "ffn_up.weight");
+                    matmul(slice_rows(w, 0, F), a, gate.data());
+                    matmul(slice_rows(w, F, 2 * (uint64_t)F), a, up.data());
+                } else {
+                    matmul(g.get(p + "ffn_gate.weight"), a, gate.data());
+                    matmul(g.get(p + "ffn_up.weight"), a, up.data());
+                }
+            }
+            prof.lap(0);
+            const int64_t nact = (int64_t)T * F;
+#pragma omp parallel for simd schedule(static) if (nact >= 16384)
+            for (int64_t i = 0; i < nact; ++i) gate[i] = gate[i] / (1.0f + std::exp(-gate[i])) * up[i];
+            prof.lap(4);
+            {
+                Act a(gate.data(), T, F);
+                matmul(g.get(p + "ffn_down.weight"), a, h.data(), true);
+            }
+            prof.lap(0);
         }
         c.len = pos0 + T;
-        if (!last) return h;
+        if (!last) { prof.report(T); return h; }
         const bool all = flags & 1u;
         const int R = all ? T : 1;
         const float* src = all ? h.data() : h.data() + (size_t)(T - 1) * E;
         std::vector<float> hn((size_t)R * E), logits((size_t)R * hp.n_vocab);
         rmsnorm(src, (const float*)g.get("output_norm.weight").data, hp.eps, R, E, hn.data());
-        matmul(g.has("output.weight") ? g.get("output.weight") : g.get("token_embd.weight"), hn.data(), R, logits.data());
+        Act a(hn.data(), R, E);
+        matmul(g.has("output.weight") ? g.get("output.weight") : g.get("token_embd.weight"), a, logits.data());
+        prof.lap(5);
+        prof.report(T);
         return logits;
     }
 };
@@ -392,7 +607,7 @@ bool serve_client(int fd, Stage& st, bool verbose) {
 int main(int argc, char** argv) {
     signal(SIGPIPE, SIG_IGN);
     std::string model, host = "127.0.0.1";
-    int port = 50052, l0 = 0, l1 = -1, n_ctx = 2048, max_seqs = 64;
+    int port = 50052, l0 = 0, l1 = -1, n_ctx = 2048, max_seqs = 64, bench_T = 0, bench_reps = 3;
     bool verbose = false;
     for (int i = 1; i < argc; ++i) {
         std::string a = argv[i];
@@ -404,12 +619,34 @@ int main(int argc, char** argv) {
         else if (a == "-c" || a == "--ctx-size") n_ctx = atoi(next().c_str());
         else if (a == "-v" || a == "--verbose") verbose = true;
         else if (a == "--max-seqs") max_seqs = std::max(1, atoi(next().c_str()));
-        else { fprintf(stderr, "dlp-worker -m model.gguf [--layers a:b] [-H host] [-p port] [-c n_ctx] [--max-seqs n] [-v]\n"); return a == "-h" ? 0 : 2; }
+        else if (a == "--bench") bench_T = atoi(next().c_str());
+        else if (a == "--bench-reps") bench_reps = std::max(1, atoi(next().c_str()));
+        else { fprintf(stderr, "dlp-worker -m model.gguf [--layers a:b] [-H host] [-p port] [-c n_ctx] [--max-seqs n] [--bench T [--bench-reps r]] [-v]\n"); return a == "-h" ? 0 : 2; }
     }
     if (model.empty()) { fprintf(stderr, "dlp-worker: -m model.gguf is required\n"); return 2; }
     Stage st;
     st.max_seqs = max_seqs;
     try { st.load(model, l0, l1, n_ctx); } catch (const std::exception& e) { fprintf(stderr, "dlp-worker: %s\n", e.what()); return 1; }
+    if (bench_T > 0) {   // no sockets: time this stage on T synthetic tokens (prefill) and on one more token (decode)
+        st.prof.on = true;
+        std::vector<uint8_t> in;
+        if (st.first) { in.resize((size_t)bench_T * 4); for (int t = 0; t < bench_T; ++t) { const int32_t id = 3 + (t * 7919) % (st.hp.n_vocab - 3); memcpy(in.data() + (size_t)t * 4, &id, 4); } }
+        else { std::vector<float> hx((size_t)bench_T * st.hp.n_embd); for (size_t i = 0; i < hx.size(); ++i) hx[i] = 0.01f * (float)((int)(i % 201) - 100); in.resize(hx.size() * 4); memcpy(in.data(), hx.data(), in.size()); }
+        const size_t per_tok = in.size() / bench_T;
+        for (int r = 0; r < bench_reps; ++r) {
+            try {
+                double t0 = omp_get_wtime();
+                st.run(1, bench_T, 0, 0, in.data(), in.size());
+                const double tp = omp_get_wtime() - t0;
+                t0 = omp_get_wtime();
+                if (bench_T < n_ctx) st.run(1, 1, bench_T, 0, in.data(), per_tok);
+                const double tg = omp_get_wtime() - t0;
+                fprintf(stderr, "bench: prefill %d tokens %.1f ms (%.1f tok/s), one decode step %.2f ms\n", bench_T, tp * 1e3, bench_T / tp, tg * 1e3);
+                st.seqs.clear();
+            } catch (const std::exception& e) { fprintf(stderr, "dlp-worker: %s\n", e.what()); return 1; }
+        }
+        return 0;
+    }
     if (host != "127.0.0.1" && host != "localhost")
         fprintf(stderr, "WARNING: listening on %s - the worker protocol is unauthenticated; never expose it to an untrusted network\n", host.c_str());
     int ls = ::socket(AF_INET, SOCK_STREAM, 0), one = 1;

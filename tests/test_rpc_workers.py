@@ -137,3 +137,42 @@ def test_other_architectures_on_cpu_workers(tmp_models, key):
                 p.wait(timeout=10)
             except Exception:
                 p.kill()
+
+
+def test_q8_0_avx2_and_vnni_kernels(tmp_models, monkeypatch):
+    """The worker picks the AVX-512 VNNI mat-mul at run time where the CPU has it; DLP_WORKER_NO_VNNI forces the AVX2 one.
+    Both (panel-blocked, 4 tokens per pass, ragged token tail by the row kernel) must match the oracle on a 13-token prompt."""
+    path = tmp_models[("tiny", "Q8_0")]
+    ref = ReferenceModel.from_gguf(path)
+    prompt = [1, 5, 9, 200, 33, 7, 8, 100, 42, 17, 300, 2, 77]
+    _, ref_logits = ref.generate_greedy(prompt, 1)
+    outs = []
+    for no_vnni in (False, True):
+        if no_vnni:
+            monkeypatch.setenv("DLP_WORKER_NO_VNNI", "1")
+        procs, eps = launch_local_workers(path, 2, base_port=_free_ports(1)[0], n_ctx=64, threads=2)
+        try:
+            eng = RpcEngine(eps, max_seqs=1)
+            sid = eng.alloc_seq()
+            outs.append(eng.prefill(sid, prompt))
+            assert nmse(ref_logits[0], outs[-1]) < 3e-4
+            for w in eng.workers:
+                w.shutdown()
+        finally:
+            for p in procs:
+                try:
+                    p.wait(timeout=10)
+                except Exception:
+                    p.kill()
+    assert nmse(outs[0], outs[1]) < 1e-8      # same int8 products, fp32 summation order differs
+
+
+def test_worker_bench_mode(tmp_models):
+    """`dlp-worker --bench T`: the stage timed locally (no sockets) with the per-phase split on stderr."""
+    import subprocess
+    from distributed_llm_pipeline_b200.runtime import native
+    native.build()
+    p = subprocess.run([native.path("dlp-worker"), "-m", tmp_models[("tiny", "Q8_0")], "-c", "64", "--bench", "16", "--bench-reps", "1"],
+                       capture_output=True, text=True, timeout=120)
+    assert p.returncode == 0, p.stderr
+    assert "bench: prefill 16 tokens" in p.stderr and "matmul" in p.stderr
