@@ -62,12 +62,17 @@ class GGMLType(enum.IntEnum):
     Q5_K = 13
     Q6_K = 14
     Q8_K = 15
+    IQ4_NL = 20
+    IQ4_XS = 23
     I8 = 24
     I16 = 25
     I32 = 26
     I64 = 27
     F64 = 28
     BF16 = 30
+    TQ1_0 = 34
+    TQ2_0 = 35
+    MXFP4 = 39
 
 
 QK_K = 256
@@ -94,6 +99,11 @@ BLOCK_GEOMETRY = {
     GGMLType.Q5_K: (256, 2 + 2 + 12 + 32 + 128),
     GGMLType.Q6_K: (256, 128 + 64 + 16 + 2),
     GGMLType.Q8_K: (256, 4 + 256 + 32),
+    GGMLType.IQ4_NL: (32, 2 + 16),
+    GGMLType.IQ4_XS: (256, 2 + 2 + 4 + 128),
+    GGMLType.TQ1_0: (256, 48 + 4 + 2),
+    GGMLType.TQ2_0: (256, 64 + 2),
+    GGMLType.MXFP4: (32, 1 + 16),
 }
 
 
@@ -107,7 +117,7 @@ def row_bytes(ggml_type: GGMLType, n_elements: int) -> int:
 
 # File-type ids written to general.file_type (llama_ftype); only those we emit.
 FTYPE = {"F32": 0, "F16": 1, "Q4_0": 2, "Q4_1": 3, "Q8_0": 7, "Q5_0": 8, "Q5_1": 9, "Q2_K": 10, "Q3_K": 12, "Q4_K_M": 15,
-         "Q5_K_M": 17, "Q6_K": 18, "BF16": 32}
+         "Q5_K_M": 17, "Q6_K": 18, "IQ4_NL": 25, "IQ4_XS": 30, "BF16": 32, "TQ1_0": 36, "TQ2_0": 37, "MXFP4_MOE": 38}
 
 
 class TokenType(enum.IntEnum):

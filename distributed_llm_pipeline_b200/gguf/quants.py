@@ -213,6 +213,75 @@ def dequant_q6_k(raw: np.ndarray) -> np.ndarray:
     return (d[:, None, None, None] * s * q.astype(np.float32)).reshape(-1)
 
 
+# ---- non-linear 4-bit, ternary and microscaling types (block layouts: ggml-common.h:236-262,416-440; value tables are part of
+# the file format: `kvalues_iq4nl`, `kvalues_mxfp4`).  Decoded to fp16 at load by the engine; no kernel reads them directly.
+
+IQ4_VALUES = np.array([-127, -104, -83, -65, -49, -35, -22, -10, 1, 13, 25, 38, 53, 69, 89, 113], np.float32)
+MXFP4_VALUES = np.array([0, 1, 2, 3, 4, 6, 8, 12, 0, -1, -2, -3, -4, -6, -8, -12], np.float32)     # E2M1 values, doubled
+
+
+def _nibble_halves(qs: np.ndarray) -> np.ndarray:
+    """[nb, n/2] bytes -> [nb, n] nibble codes: element j is the low nibble of byte j, element j + n/2 the high nibble."""
+    return np.concatenate([qs & 0x0F, qs >> 4], axis=-1)
+
+
+def dequant_iq4_nl(raw: np.ndarray) -> np.ndarray:
+    b = _blocks(raw, GGMLType.IQ4_NL)
+    d = _f16(b[:, 0:2])[:, None]
+    return (d * IQ4_VALUES[_nibble_halves(b[:, 2:18])]).reshape(-1)
+
+
+def dequant_iq4_xs(raw: np.ndarray) -> np.ndarray:
+    b = _blocks(raw, GGMLType.IQ4_XS)
+    d = _f16(b[:, 0:2])[:, None]
+    sh = b[:, 2:4].copy().view("<u2").astype(np.uint32)                      # [nb, 1]: two high bits per sub-block
+    sl = b[:, 4:8]
+    lo = np.stack([sl & 0x0F, sl >> 4], axis=-1).reshape(-1, 8).astype(np.uint32)
+    hi = (sh >> (2 * np.arange(8, dtype=np.uint32))[None, :]) & 3
+    ls = (lo | (hi << 4)).astype(np.float32) - 32.0                          # 6-bit sub-block scale, offset 32
+    codes = _nibble_halves(b[:, 8:136].reshape(-1, 8, 16))                   # [nb, 8, 32]
+    return ((d * ls)[:, :, None] * IQ4_VALUES[codes]).reshape(-1)
+
+
+def dequant_tq2_0(raw: np.ndarray) -> np.ndarray:
+    b = _blocks(raw, GGMLType.TQ2_0)
+    d = _f16(b[:, 64:66])[:, None]
+    qs = b[:, 0:64].reshape(-1, 2, 1, 32)                                    # two groups of 32 bytes, four 2-bit planes each
+    q = (qs >> (2 * np.arange(4, dtype=np.uint8)).reshape(1, 1, 4, 1)) & 3
+    return (d * (q.reshape(-1, 256).astype(np.float32) - 1.0)).reshape(-1)
+
+
+_POW3 = np.array([1, 3, 9, 27, 81, 243], np.uint8)
+
+
+def dequant_tq1_0(raw: np.ndarray) -> np.ndarray:
+    """Five trits per byte in base 3 (the byte is the fixed-point fraction trits / 3^5): multiplying by 3^n modulo 256 moves
+    trit n to the top, `* 3 >> 8` reads it."""
+    b = _blocks(raw, GGMLType.TQ1_0)
+    d = _f16(b[:, 52:54])[:, None]
+
+    def trits(bytes_: np.ndarray, n: int) -> np.ndarray:                    # [nb, m] -> [nb, n, m]
+        q = (bytes_[:, None, :] * _POW3[:n].reshape(1, n, 1)).astype(np.uint8)
+        return ((q.astype(np.uint16) * 3) >> 8).astype(np.float32)
+
+    parts = [trits(b[:, 0:32], 5).reshape(-1, 160), trits(b[:, 32:48], 5).reshape(-1, 80), trits(b[:, 48:52], 4).reshape(-1, 16)]
+    return (d * (np.concatenate(parts, axis=1) - 1.0)).reshape(-1)
+
+
+def e8m0_to_f32_half(e: np.ndarray) -> np.ndarray:
+    """Shared MX exponent -> 2^(e - 128) (half the E8M0 value, because the value table holds doubled E2M1 numbers)."""
+    e = e.astype(np.uint32)
+    bits = np.where(e < 2, np.uint32(0x00200000) << e, (e - 1) << 23).astype(np.uint32)
+    return bits.view(np.float32)
+
+
+def dequant_mxfp4(raw: np.ndarray) -> np.ndarray:
+    b = _blocks(raw, GGMLType.MXFP4)
+    d = e8m0_to_f32_half(b[:, 0:1])
+    return (d * MXFP4_VALUES[_nibble_halves(b[:, 1:17])]).reshape(-1)
+
+
+
 def dequantize(raw: np.ndarray, ggml_type: GGMLType, shape: tuple[int, ...] | None = None) -> np.ndarray:
     """Decode a raw byte buffer of `ggml_type` to float32 (optionally reshaped, row-major)."""
     t = GGMLType(ggml_type)
@@ -243,6 +312,16 @@ def dequantize(raw: np.ndarray, ggml_type: GGMLType, shape: tuple[int, ...] | No
         out = dequant_q5_k(raw)
     elif t == GGMLType.Q6_K:
         out = dequant_q6_k(raw)
+    elif t == GGMLType.IQ4_NL:
+        out = dequant_iq4_nl(raw)
+    elif t == GGMLType.IQ4_XS:
+        out = dequant_iq4_xs(raw)
+    elif t == GGMLType.TQ1_0:
+        out = dequant_tq1_0(raw)
+    elif t == GGMLType.TQ2_0:
+        out = dequant_tq2_0(raw)
+    elif t == GGMLType.MXFP4:
+        out = dequant_mxfp4(raw)
     else:
         raise NotImplementedError(f"dequantize: unsupported type {t!r}")
     return out.reshape(shape) if shape is not None else out
@@ -470,6 +549,105 @@ def quant_q6_k(x: np.ndarray) -> np.ndarray:
     return out.reshape(-1)
 
 
+def _nearest_code(v: np.ndarray, table: np.ndarray) -> np.ndarray:
+    """Index of the table entry closest to each value (first one on ties)."""
+    return np.abs(v[..., None] - table).argmin(-1).astype(np.uint8)
+
+
+def _signed_max(x: np.ndarray) -> np.ndarray:
+    """The element of largest magnitude along the last axis, with its sign."""
+    i = np.abs(x).argmax(-1)
+    return np.take_along_axis(x, i[..., None], -1)[..., 0]
+
+
+def _pack_nibble_halves(codes: np.ndarray) -> np.ndarray:
+    h = codes.shape[-1] // 2
+    return (codes[..., :h] | (codes[..., h:] << 4)).astype(np.uint8)
+
+
+def quant_iq4_nl(x: np.ndarray) -> np.ndarray:
+    """The value table is asymmetric (-127 .. 113): the element of largest magnitude is mapped onto -127 by letting the block
+    scale carry its sign; every other element takes the nearest table value."""
+    xb = x.reshape(-1, 32)
+    d = (_signed_max(xb) / -127.0).astype(np.float16)
+    df = d.astype(np.float32)
+    inv = np.where(df != 0, 1.0 / np.where(df != 0, df, 1), 0).astype(np.float32)
+    out = np.empty((xb.shape[0], 18), np.uint8)
+    out[:, 0:2] = d.view(np.uint8).reshape(-1, 2)
+    out[:, 2:] = _pack_nibble_halves(_nearest_code(xb * inv[:, None], IQ4_VALUES))
+    return out.reshape(-1)
+
+
+def quant_iq4_xs(x: np.ndarray) -> np.ndarray:
+    """Eight 32-value sub-blocks share an fp16 scale; each has a signed 6-bit multiplier (stored + 32)."""
+    xb = x.reshape(-1, 8, 32)
+    dl = _signed_max(xb) / -127.0                                            # ideal sub-block scales [nb, 8]
+    big = _signed_max(dl)
+    d = (big / -32.0).astype(np.float16)                                      # the largest one lands on multiplier -32
+    df = d.astype(np.float32)
+    inv_d = np.where(df != 0, 1.0 / np.where(df != 0, df, 1), 0).astype(np.float32)
+    ls = np.clip(_nearest_int(dl * inv_d[:, None]), -32, 31).astype(np.int32)
+    sub = df[:, None] * ls
+    inv = np.where(sub != 0, 1.0 / np.where(sub != 0, sub, 1), 0).astype(np.float32)
+    codes = _nearest_code(xb * inv[:, :, None], IQ4_VALUES)
+    u = (ls + 32).astype(np.uint32)
+    out = np.empty((xb.shape[0], 136), np.uint8)
+    out[:, 0:2] = d.view(np.uint8).reshape(-1, 2)
+    sh = ((u >> 4) << (2 * np.arange(8, dtype=np.uint32))[None, :]).sum(-1).astype("<u2")
+    out[:, 2:4] = sh.view(np.uint8).reshape(-1, 2)
+    lo = (u & 0x0F).astype(np.uint8).reshape(-1, 4, 2)
+    out[:, 4:8] = lo[:, :, 0] | (lo[:, :, 1] << 4)
+    out[:, 8:] = _pack_nibble_halves(codes).reshape(-1, 128)
+    return out.reshape(-1)
+
+
+def _ternary(x: np.ndarray):
+    xb = x.reshape(-1, 256)
+    d = np.abs(xb).max(-1).astype(np.float16)
+    df = d.astype(np.float32)
+    inv = np.where(df != 0, 1.0 / np.where(df != 0, df, 1), 0).astype(np.float32)
+    return d, (np.clip(_nearest_int(xb * inv[:, None]), -1, 1) + 1).astype(np.uint8)
+
+
+def quant_tq2_0(x: np.ndarray) -> np.ndarray:
+    d, q = _ternary(x)
+    planes = q.reshape(-1, 2, 4, 32)
+    out = np.empty((q.shape[0], 66), np.uint8)
+    out[:, 0:64] = (planes << (2 * np.arange(4, dtype=np.uint8)).reshape(1, 1, 4, 1)).sum(2).astype(np.uint8).reshape(-1, 64)
+    out[:, 64:66] = d.view(np.uint8).reshape(-1, 2)
+    return out.reshape(-1)
+
+
+def quant_tq1_0(x: np.ndarray) -> np.ndarray:
+    d, q = _ternary(x)
+
+    def pack(trits: np.ndarray) -> np.ndarray:                              # [nb, n, m] -> [nb, m]; trit 0 is the most significant
+        n = trits.shape[1]
+        v = (trits.astype(np.uint32) * (3 ** (4 - np.arange(n, dtype=np.uint32))).reshape(1, n, 1)).sum(1)
+        return ((v * 256 + 242) // 243).astype(np.uint8)                    # ceil(v * 256 / 243): the byte as a base-3 fraction
+
+    out = np.empty((q.shape[0], 54), np.uint8)
+    out[:, 0:32] = pack(q[:, 0:160].reshape(-1, 5, 32))
+    out[:, 32:48] = pack(q[:, 160:240].reshape(-1, 5, 16))
+    out[:, 48:52] = pack(q[:, 240:256].reshape(-1, 4, 4))
+    out[:, 52:54] = d.view(np.uint8).reshape(-1, 2)
+    return out.reshape(-1)
+
+
+def quant_mxfp4(x: np.ndarray) -> np.ndarray:
+    """Shared power-of-two scale per 32 values chosen so the largest magnitude falls in the top binade of E2M1 (4 .. 6)."""
+    xb = x.reshape(-1, 32)
+    amax = np.abs(xb).max(-1)
+    e = np.where(amax > 0, np.floor(np.log2(np.where(amax > 0, amax, 1))) - 2 + 127, 0)
+    e = np.clip(e, 0, 254).astype(np.uint8)
+    d = e8m0_to_f32_half(e)
+    out = np.empty((xb.shape[0], 17), np.uint8)
+    out[:, 0] = e
+    out[:, 1:] = _pack_nibble_halves(_nearest_code(xb / d[:, None], MXFP4_VALUES))
+    return out.reshape(-1)
+
+
+
 def quantize(x: np.ndarray, ggml_type: GGMLType) -> np.ndarray:
     """Encode float32 data (last dim multiple of block size) -> raw uint8 bytes."""
     t = GGMLType(ggml_type)
@@ -494,6 +672,11 @@ def quantize(x: np.ndarray, ggml_type: GGMLType) -> np.ndarray:
         GGMLType.Q4_K: quant_q4_k,
         GGMLType.Q5_K: quant_q5_k,
         GGMLType.Q6_K: quant_q6_k,
+        GGMLType.IQ4_NL: quant_iq4_nl,
+        GGMLType.IQ4_XS: quant_iq4_xs,
+        GGMLType.TQ1_0: quant_tq1_0,
+        GGMLType.TQ2_0: quant_tq2_0,
+        GGMLType.MXFP4: quant_mxfp4,
     }.get(t)
     if fn is None:
         raise NotImplementedError(f"quantize: unsupported type {t!r}")

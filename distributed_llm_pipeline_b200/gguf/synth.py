@@ -61,6 +61,16 @@ def tensor_type_for(name: str, ftype: str, i_layer: int, cfg: ModelConfig) -> GG
         if ".ffn_down" in name and use_more_bits(i_layer, cfg.n_layer):
             return GGMLType.Q6_K
         return base
+    if ftype in ("IQ4_NL", "IQ4_XS", "TQ1_0", "TQ2_0"):     # decoded to fp16 at load; embeddings / output keep more bits as in the reference
+        if name == "output.weight":
+            return GGMLType.Q6_K
+        if name == "token_embd.weight":
+            return GGMLType.Q4_K if ftype.startswith("TQ") else GGMLType[ftype]
+        if ftype == "IQ4_XS" and ".attn_v." in name and cfg.n_expert == 0 and use_more_bits(i_layer, cfg.n_layer):
+            return GGMLType.Q5_K
+        return GGMLType[ftype]
+    if ftype == "MXFP4_MOE":                                # expert matrices in MXFP4, everything else Q8_0 (llama-quant.cpp)
+        return GGMLType.MXFP4 if "_exps." in name else GGMLType.Q8_0
     raise ValueError(f"unknown file type {ftype!r}")
 
 

@@ -12,7 +12,8 @@ from gguf import quants as GQ  # noqa: E402
 
 TYPES = [(GGMLType.Q8_0, 3e-5), (GGMLType.Q4_0, 1e-2), (GGMLType.Q4_K, 1e-2), (GGMLType.Q5_K, 3e-3), (GGMLType.Q6_K, 1e-3),
          (GGMLType.F16, 1e-6), (GGMLType.BF16, 1e-4), (GGMLType.Q4_1, 1e-2), (GGMLType.Q5_0, 3e-3), (GGMLType.Q5_1, 3e-3),
-         (GGMLType.Q2_K, 0.2), (GGMLType.Q3_K, 5e-2)]
+         (GGMLType.Q2_K, 0.2), (GGMLType.Q3_K, 5e-2), (GGMLType.IQ4_NL, 1e-2), (GGMLType.IQ4_XS, 1e-2), (GGMLType.MXFP4, 2e-2),
+         (GGMLType.TQ1_0, 0.7), (GGMLType.TQ2_0, 0.7)]
 
 
 @pytest.mark.parametrize("t,tol", TYPES)
@@ -48,6 +49,31 @@ def test_low_bit_k_decoders_on_arbitrary_blocks(t, fields):
     assert np.allclose(dequantize(raw, t), ref, rtol=0, atol=1e-7)
 
 
+@pytest.mark.parametrize("t,f16_cols", [(GGMLType.IQ4_NL, [0]), (GGMLType.IQ4_XS, [0]), (GGMLType.TQ1_0, [52]), (GGMLType.TQ2_0, [64]),
+                                        (GGMLType.MXFP4, [])])
+def test_4bit_ternary_mx_decoders_on_arbitrary_blocks(t, f16_cols):
+    """Random bytes in every packed field (scales pinned finite; every MX exponent 0..253) decode exactly as gguf-py does."""
+    from distributed_llm_pipeline_b200.gguf.constants import BLOCK_GEOMETRY
+    rng = np.random.default_rng(5)
+    nbytes = BLOCK_GEOMETRY[t][1]
+    raw = rng.integers(0, 256, size=(254, nbytes), dtype=np.uint8)
+    for col in f16_cols:
+        raw[:, col:col + 2] = np.array([0.0123], np.float16).view(np.uint8)
+    if t == GGMLType.MXFP4:
+        raw[:, 0] = np.arange(254)
+    ref = GQ.dequantize(raw.reshape(1, -1), gguf.GGMLQuantizationType(int(t))).reshape(-1)
+    assert np.array_equal(dequantize(raw, t), ref)
+
+
+@pytest.mark.parametrize("t", [GGMLType.TQ1_0, GGMLType.TQ2_0])
+def test_ternary_encoders_are_bit_exact_with_gguf_py(t):
+    rng = np.random.default_rng(6)
+    x = rng.integers(-1, 2, (8, 512)).astype(np.float32) * 0.25
+    ref = GQ.quantize(x, gguf.GGMLQuantizationType(int(t)))
+    assert np.array_equal(quantize(x, t).reshape(ref.shape), ref)
+    assert np.array_equal(dequantize(quantize(x, t), t, x.shape), x)      # ternary data is represented exactly
+
+
 @pytest.mark.parametrize("t", [GGMLType.Q8_0, GGMLType.Q4_K, GGMLType.Q5_K, GGMLType.Q6_K])
 def test_random_blocks_are_valid(t):
     rng = np.random.default_rng(1)
@@ -66,7 +92,7 @@ def test_scale_min_pack_roundtrip():
     assert np.array_equal(sc, s2) and np.array_equal(mn, m2)
 
 
-@pytest.mark.parametrize("ftype", ["F16", "Q8_0", "Q4_K_M", "Q5_1", "Q3_K"])
+@pytest.mark.parametrize("ftype", ["F16", "Q8_0", "Q4_K_M", "Q5_1", "Q3_K", "IQ4_XS", "TQ1_0"])
 def test_synthetic_file_readable_by_reference_reader(tmp_path, ftype):
     cfg = preset("tiny")
     path = write_synthetic_gguf(str(tmp_path / "m.gguf"), cfg, ftype)
