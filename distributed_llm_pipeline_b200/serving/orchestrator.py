@@ -195,6 +195,7 @@ class Orchestrator:
                 ids = [fim["pre"]] + t.encode(d.get("input_prefix", ""), add_bos=False) + [fim["suf"]] + \
                     t.encode(d.get("input_suffix", ""), add_bos=False) + [fim["mid"]]
                 d["prompt"] = ([t.bos_id] if t.add_bos else []) + ids
+                d.setdefault("infill_sampler", True)      # the reference's /infill runs the infill sampler at the end of its chain
                 return await self.completion(d, writer)
             if method == "POST" and path in ("/completion", "/completions", "/v1/completions"):
                 return await self.completion(json.loads(body or b"{}"), writer, openai=path.startswith("/v1"))
@@ -229,6 +230,8 @@ class Orchestrator:
                     await self._json(writer, [{"index": i, "embedding": v} for i, v in enumerate(vecs)] if isinstance(inp, list) and items is inp
                                      else {"embedding": vecs[0]})
                 return True
+            if method == "POST" and path in ("/rerank", "/reranking", "/v1/rerank", "/v1/reranking"):
+                return await self.rerank(json.loads(body or b"{}"), writer)
             if method == "GET" and path == "/health":
                 await self._json(writer, {"status": "ok"})
                 return True
@@ -383,6 +386,7 @@ class Orchestrator:
         if schema is None and rf.get("type") == "json_schema":
             schema = (rf.get("json_schema") or {}).get("schema") or {}
         return SamplingParams(grammar=str(d.get("grammar", "") or ""), json_schema=schema,
+                              infill=bool(d.get("infill_sampler", False)) or "infill" in (d.get("samplers") or []),
                               top_n_sigma=float(d.get("top_n_sigma", -1.0)), dynatemp_range=float(d.get("dynatemp_range", 0.0)),
                               dynatemp_exponent=float(d.get("dynatemp_exponent", 1.0)), xtc_probability=float(d.get("xtc_probability", 0.0)),
                               xtc_threshold=float(d.get("xtc_threshold", 0.1)), mirostat=int(d.get("mirostat", 0)),
@@ -430,30 +434,88 @@ class Orchestrator:
                                       "tokens_evaluated": len(req.prompt_ids), "timings": req.timings()})
         return True
 
+    async def rerank(self, d: dict, writer) -> bool:
+        """`/v1/rerank` (tools/server/server.cpp rerank handler: `{"query", "documents", "top_n"}` -> results sorted by
+        `relevance_score`).  The reference scores with a classification-head reranker (pooling type RANK); the decoder families
+        served here have no such head, so the score is the cosine similarity of the pooled embeddings of query and document -
+        the same engine path as `/v1/embeddings` - which keeps the route and its wire format usable with any loaded model."""
+        query, docs = d.get("query"), d.get("documents") or d.get("texts")
+        if not isinstance(query, str) or not isinstance(docs, list) or not docs:
+            await self._json(writer, {"error": {"message": '"query" (string) and "documents" (non-empty array) are required', "type": "invalid_request_error"}},
+                             "400 Bad Request")
+            return True
+        docs = [x if isinstance(x, str) else str(x.get("text", "")) if isinstance(x, dict) else str(x) for x in docs]
+        pooling = str(d.get("pooling", "mean"))
+        loop = asyncio.get_running_loop()
+        qv = await loop.run_in_executor(None, self.sched.embed, query, pooling)
+        n_tok = len(self.sched.tok.encode(query))
+        scored = []
+        for i, doc in enumerate(docs):
+            dv = await loop.run_in_executor(None, self.sched.embed, doc, pooling)
+            n_tok += len(self.sched.tok.encode(doc))
+            scored.append({"index": i, "relevance_score": float(sum(a * b for a, b in zip(qv, dv)))})     # both vectors are unit length
+        scored.sort(key=lambda r: -r["relevance_score"])
+        top_n = int(d.get("top_n", len(scored)) or len(scored))
+        results = scored[:max(1, top_n)]
+        if d.get("return_documents") or d.get("return_text"):
+            for r in results:
+                r["document"] = {"text": docs[r["index"]]}
+        await self._json(writer, {"model": str(d.get("model") or self.info.get("name", "model")), "object": "list",
+                                  "usage": {"prompt_tokens": n_tok, "total_tokens": n_tok}, "results": results})
+        return True
+
     async def chat_completions(self, d: dict, writer) -> bool:
-        prompt = apply_chat_template(self.info.get("metadata", {}), d.get("messages", []))
+        from . import toolcall
+        tools = d.get("tools") or []
+        setup = toolcall.prepare(d.get("messages", []), tools, d.get("tool_choice", "auto"), bool(d.get("parallel_tool_calls", False)))
+        prompt = apply_chat_template(self.info.get("metadata", {}), setup.messages)
         n_predict = int(d.get("max_tokens", d.get("max_completion_tokens", self.n_predict)))
         stop = d.get("stop") or []
-        req = Request(prompt=prompt, n_predict=n_predict, sampling=self._sampling_from(d), stop=[stop] if isinstance(stop, str) else list(stop))
+        sampling = self._sampling_from(d)
+        if setup.active and sampling.json_schema is None and not sampling.grammar:
+            sampling.json_schema = setup.json_schema         # the generic tool-call envelope (common/chat.cpp, generic handler)
+        req = Request(prompt=prompt, n_predict=n_predict, sampling=sampling, stop=[stop] if isinstance(stop, str) else list(stop))
         rid = "chatcmpl-" + uuid.uuid4().hex[:24]
+        model = self.info.get("name", "model")
         if d.get("stream"):
             writer.write(self._head("200 OK", [("content-type", "text/event-stream"), ("cache-control", "no-cache")] + CORS + [("connection", "close")]))
+            held: list[str] = []
+
+            def chunk(delta, finish):
+                base = {"id": rid, "object": "chat.completion.chunk", "created": int(time.time()), "model": model,
+                        "choices": [{"index": 0, "delta": delta, "finish_reason": finish}]}
+                return b"data: " + json.dumps(base).encode() + b"\n\n"
 
             def fmt(kind, content):
-                base = {"id": rid, "object": "chat.completion.chunk", "created": int(time.time()), "model": self.info.get("name", "model")}
                 if kind == "token":
-                    base["choices"] = [{"index": 0, "delta": {"content": content}, "finish_reason": None}]
-                    return b"data: " + json.dumps(base).encode() + b"\n\n"
+                    if tools:                     # a tool call is only known once the answer is complete: hold the text back
+                        held.append(content)
+                        return None
+                    return chunk({"content": content}, None)
                 if kind == "done":
-                    base["choices"] = [{"index": 0, "delta": {}, "finish_reason": content}]
-                    return b"data: " + json.dumps(base).encode() + b"\n\ndata: [DONE]\n\n"
+                    out = b""
+                    reason = content
+                    if tools:
+                        msg = toolcall.parse("".join(held), tools)
+                        if msg.tool_calls:
+                            out += chunk({"role": "assistant", "tool_calls": [{"index": i, **c} for i, c in enumerate(msg.tool_calls)]}, None)
+                            reason = "tool_calls"
+                        if msg.content:
+                            out += chunk({"content": msg.content}, None)
+                    return out + chunk({}, reason) + b"data: [DONE]\n\n"
                 return None
 
             await self._stream_request(req, writer, fmt)
             return False
         await self._run_blocking(req)
-        await self._json(writer, {"id": rid, "object": "chat.completion", "created": int(time.time()), "model": self.info.get("name", "model"),
-                                  "choices": [{"index": 0, "message": {"role": "assistant", "content": req.text}, "finish_reason": req.finish_reason}],
+        message, reason = {"role": "assistant", "content": req.text}, req.finish_reason
+        if tools:
+            msg = toolcall.parse(req.text, tools)
+            message = msg.to_openai()
+            if msg.tool_calls:
+                reason = "tool_calls"
+        await self._json(writer, {"id": rid, "object": "chat.completion", "created": int(time.time()), "model": model,
+                                  "choices": [{"index": 0, "message": message, "finish_reason": reason}],
                                   "usage": {"prompt_tokens": len(req.prompt_ids), "completion_tokens": len(req.output_ids),
                                             "total_tokens": len(req.prompt_ids) + len(req.output_ids)}, "timings": req.timings()})
         return True
@@ -666,12 +728,18 @@ def add_parallel_args(ap):
     ap.add_argument("--workers", type=int, default=0, help="launch this many local dlp-worker stages and use them (implies --rpc)")
     ap.add_argument("--worker-base-port", type=int, default=50052)
     ap.add_argument("--no-warmup", action="store_true", help="skip the start-up warm-up (kernel set-up + decode-graph capture per batch size)")
+    ap.add_argument("-md", "--model-draft", default=os.environ.get("DLP_ARG_MODEL_DRAFT"),
+                    help="draft model (same vocabulary) for speculative decoding of greedy requests inside the server")
+    ap.add_argument("--draft-max", type=int, default=16, help="tokens drafted per verification block (0 = off unless the request asks)")
 
 
 def build_service(model: str, device: str = "cuda", n_ctx: int = 2048, n_slots: int = 4, n_batch: int = 2048, page_size: int = 64,
                   lora=None, pp: int = 1, tp: int = 1, tp_impl: str = "fused", tensor_split=None, rpc: str | None = None,
-                  workers: int = 0, worker_base_port: int = 50052):
+                  workers: int = 0, worker_base_port: int = 50052, model_draft: str | None = None, draft_max: int = 16):
     """Load a GGUF checkpoint and return (scheduler, model_info, startup_logs).
+
+    model_draft: a second, smaller checkpoint with the same vocabulary, loaded on the front-end process's device; greedy requests
+    are then decoded by draft-and-verify blocks (`llama-server -md`, tools/server/server-context.cpp:2029-2068).
 
     pp * tp > 1: must run under torchrun (one process per rank); only the leader rank returns - followers replay the leader's
     engine calls inside this function until the service shuts down and then exit (parallel/spmd.py).
@@ -739,13 +807,24 @@ def build_service(model: str, device: str = "cuda", n_ctx: int = 2048, n_slots: 
             "metadata": {"tokenizer.chat_template": f.metadata.get("tokenizer.chat_template", ""),
                          "bos_token": tok.tokens[tok.bos_id] if 0 <= tok.bos_id < tok.n_vocab else "",
                          "eos_token": tok.tokens[tok.eos_id] if 0 <= tok.eos_id < tok.n_vocab else ""}, **info_extra}
-    sched = Scheduler(eng, tok, n_batch=n_batch, n_slots=n_slots)
+    draft_eng = None
+    if model_draft:
+        fd = open_gguf(model_draft)
+        tok_d = Tokenizer(fd.metadata)
+        if tok_d.n_vocab != tok.n_vocab or tok_d.tokens[:256] != tok.tokens[:256]:     # common/speculative.cpp: vocabularies must match
+            raise ValueError(f"draft model vocabulary ({tok_d.n_vocab} tokens) does not match the target's ({tok.n_vocab})")
+        wd = load_weights(fd, dev)
+        draft_eng = LlamaEngine(wd, n_ctx=n_ctx, max_seqs=n_slots + 1, page_size=page_size if dev != "cpu" else 16,
+                                max_batch_tokens=min(n_batch, 512))
+        logs.append(f"draft model: {os.path.basename(model_draft)} | {wd.cfg.n_layer} layers | n_embd {wd.cfg.n_embd} | up to {draft_max} tokens per block\n")
+        info["draft_model"] = os.path.basename(model_draft)
+    sched = Scheduler(eng, tok, n_batch=n_batch, n_slots=n_slots, draft_engine=draft_eng, n_draft_default=draft_max if draft_eng else 0)
     return sched, info, logs
 
 
 def service_kwargs(a) -> dict:
     return dict(pp=a.pp, tp=a.tp, tp_impl=a.tp_impl, tensor_split=a.tensor_split, rpc=a.rpc, workers=a.workers,
-                worker_base_port=a.worker_base_port)
+                worker_base_port=a.worker_base_port, model_draft=getattr(a, "model_draft", None), draft_max=getattr(a, "draft_max", 16))
 
 
 def maybe_reexec(a, module: str, argv):

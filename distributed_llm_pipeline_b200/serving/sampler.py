@@ -41,13 +41,14 @@ class SamplingParams:
     dry_breakers: tuple = ()           # token ids that end a repeated span (the reference's sequence breakers, tokenised)
     grammar: str = ""                  # GBNF text; "" = unconstrained
     json_schema: dict | None = None    # converted to GBNF when `grammar` is empty
+    infill: bool = False               # fill-in-the-middle filter: prefer ending over low-confidence text, merge prefix-sharing tokens
 
     @property
     def host_only(self) -> bool:
         """True when the chain needs a sampler the device kernel does not implement."""
         return bool(self.repeat_penalty != 1.0 or self.frequency_penalty or self.presence_penalty or self.logit_bias
                     or self.typical_p < 1.0 or self.top_n_sigma > 0 or self.dynatemp_range > 0 or self.xtc_probability > 0
-                    or self.mirostat or self.grammar or self.json_schema is not None or self.dry_multiplier > 0)
+                    or self.mirostat or self.grammar or self.json_schema is not None or self.dry_multiplier > 0 or self.infill)
 
     @property
     def greedy(self) -> bool:
@@ -139,6 +140,57 @@ def sample_reference(logits: torch.Tensor, top_k: int, top_p: float, min_p: floa
     return torch.tensor(out, dtype=torch.int32)
 
 
+def apply_infill(row: torch.Tensor, pieces: list, eog_ids, eot_id: int, n_cand: int = 64) -> torch.Tensor:
+    """Fill-in-the-middle candidate filter (`llama_sampler_init_infill`, llama-sampling.cpp:3495-3670), on the `n_cand` most likely
+    tokens (the reference runs it after top-k):
+
+    1. when the end-of-generation mass is not negligible against the text mass (3 * p_eog * n > p_txt) only the EOG tokens stay:
+       an infill should stop rather than ramble;
+    2. a token whose text is a prefix of another candidate's text describes the same continuation: each such pair is merged into
+       its more likely member (its probability gains the other's);
+    3. text tokens below 0.2 are dropped; nothing left -> end of text; after renormalising, those below 1 / (n_text + 1) go too.
+
+    Returns logits (log-probabilities of the survivors, -inf elsewhere)."""
+    V = row.numel()
+    probs = torch.softmax(row.float(), -1)
+    vals, ids = probs.topk(min(n_cand, V))
+    ids_l, p = ids.tolist(), vals.clone()
+    p = p / p.sum()
+    is_eog = torch.tensor([i in eog_ids for i in ids_l])
+    out = torch.full_like(row, float("-inf"), dtype=torch.float32)
+    p_eog, p_txt = float(p[is_eog].sum()), float(p[~is_eog].sum())
+    if 3.0 * p_eog * len(ids_l) > p_txt:
+        keep = ids[is_eog]
+        out[keep] = torch.log(p[is_eog] / p_eog)
+        return out
+    text = [pieces[i] if (i < len(pieces) and pieces[i]) else "" for i in ids_l]
+    alive = [True] * len(ids_l)
+    pl = p.tolist()
+    for i0 in range(len(ids_l)):
+        for i1 in range(len(ids_l)):
+            if not alive[i0]:
+                break
+            if i0 == i1 or not alive[i1]:
+                continue
+            if text[i0] and text[i1].startswith(text[i0]):
+                dst, src = (i1, i0) if pl[i1] > pl[i0] else (i0, i1)
+                pl[dst] += pl[src]
+                pl[src], alive[src] = 0.0, False
+    eog_l = is_eog.tolist()
+    kept = [i for i in range(len(ids_l)) if alive[i] and (eog_l[i] or pl[i] >= 0.2)]
+    n_txt = sum(1 for i in kept if not eog_l[i])
+    if n_txt == 0:
+        out[eot_id] = 0.0
+        return out
+    tot = sum(pl[i] for i in kept)
+    thold = 1.0 / (n_txt + 1)
+    kept = [i for i in kept if eog_l[i] or pl[i] / tot >= thold]
+    tot2 = sum(pl[i] for i in kept)
+    for i in kept:
+        out[ids_l[i]] = float(torch.log(torch.tensor(pl[i] / tot2))) if pl[i] > 0 else float("-inf")
+    return out
+
+
 class Sampler:
     """Stateful per-request sampler (history for penalties, private RNG stream)."""
 
@@ -148,6 +200,12 @@ class Sampler:
         self.gen = torch.Generator().manual_seed(params.seed)
         self.mu = 2.0 * params.mirostat_tau
         self.constraint = None
+        self._infill = None
+        if params.infill:
+            if tokenizer is None:
+                raise ValueError("the infill sampler needs the tokenizer")
+            eot = int(tokenizer.eot_id) if tokenizer.eot_id is not None else int(tokenizer.eos_id)
+            self._infill = (tokenizer.token_texts(), set(int(i) for i in tokenizer.stop_ids), eot)
         gtext = params.grammar
         if not gtext and params.json_schema is not None:
             from .grammar import json_schema_to_gbnf
@@ -227,6 +285,8 @@ class Sampler:
                 row[tid] += bias
         row = apply_penalties(row, self.history, p)
         row = apply_dry(row, self.history, p)
+        if self._infill is not None:
+            row = apply_infill(row, *self._infill, n_cand=max(p.top_k, 1) if p.top_k > 0 else 64)
         tok = self._pick(row)
         if self.constraint is not None and not self.constraint.allowed(tok):
             # the unconstrained pick breaks the grammar: mask the whole vocabulary and pick again (the reference checks

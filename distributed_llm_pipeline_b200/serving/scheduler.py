@@ -131,8 +131,13 @@ class Scheduler:
     """Owns the engine; `step()` advances every active slot by one scheduling quantum."""
 
     def __init__(self, engine, tokenizer: Tokenizer, n_batch: int | None = None, log: Callable[[str], None] | None = None,
-                 n_slots: int | None = None):
+                 n_slots: int | None = None, draft_engine=None, n_draft_default: int = 0):
         self.eng, self.tok = engine, tokenizer
+        # `-md / --model-draft`: a smaller engine with the same vocabulary proposes tokens, the target verifies a whole block in
+        # one forward (server-context.cpp:2029-2068 + common/speculative.cpp).  One draft sequence per slot, kept in step with it.
+        self.draft_eng = draft_engine
+        self.n_draft_default = n_draft_default or (16 if draft_engine is not None else 0)
+        self._drafters: dict[int, object] = {}
         self.n_slots = min(n_slots or engine.max_seqs, engine.max_seqs)
         self.n_batch = min(n_batch or engine.max_tokens, engine.max_tokens)
         self.slots = [Slot(i) for i in range(self.n_slots)]
@@ -341,12 +346,25 @@ class Scheduler:
         for every position; the longest prefix the model agrees with is accepted.  Returns False when the slot should take the
         normal batched decode step instead (no draft found, sampling is not greedy, engine cannot return all logits)."""
         req = s.req
-        if req.n_draft <= 0 or not req.sampling.greedy or req.sampling.host_only or not hasattr(self.eng, "copy_seq"):
+        n_draft = req.n_draft if req.n_draft > 0 else (self.n_draft_default if req.n_draft == 0 else 0)     # n_draft < 0: off for this request
+        if n_draft <= 0 or not req.sampling.greedy or req.sampling.host_only or not hasattr(self.eng, "copy_seq"):
             return False
-        from .speculative import NgramDrafter
+        from .speculative import ModelDrafter, NgramDrafter
         history = s.cache_tokens + [s.next_token]
-        room = min(req.n_draft, req.n_predict - len(req.output_ids), self.eng.n_ctx - len(history) - 2, self.eng.max_tokens - 1)
-        draft = NgramDrafter().draft(history, room) if room > 0 else []
+        room = min(n_draft, req.n_predict - len(req.output_ids), self.eng.n_ctx - len(history) - 2, self.eng.max_tokens - 1)
+        draft: list[int] = []
+        if room > 0 and self.draft_eng is not None and len(history) + room < self.draft_eng.n_ctx:
+            d = self._drafters.get(s.idx)
+            if d is None:
+                d = self._drafters[s.idx] = ModelDrafter(self.draft_eng)
+                d.start(history)
+            try:
+                draft = d.draft(history, room)
+            except (RuntimeError, NotImplementedError) as e:     # the draft model must never take the request down with it
+                self.log(f"draft model failed ({e}); continuing without it for slot {s.idx}")
+                draft = []
+        elif room > 0:
+            draft = NgramDrafter().draft(history, room)
         if not draft:
             return False
         t0 = time.time()
@@ -373,6 +391,9 @@ class Scheduler:
             self._accept(s, int(pred[n_ok]))                           # the model's own next token becomes the pending one
         if s.sid is not None and self.eng.seq_len(s.sid) != len(s.cache_tokens):
             self.eng.truncate_seq(s.sid, len(s.cache_tokens))          # finished inside the block: cache mirrors cache_tokens again
+        d = self._drafters.get(s.idx)
+        if d is not None:
+            d.accept(len(history) + n_ok)                              # the draft cache keeps the agreed prefix only
         return True
 
     def _device_samplable(self, s: Slot) -> bool:
@@ -434,6 +455,7 @@ class Scheduler:
                                f"{t['prompt_per_second']} tok/s | eval {t['predicted_n']} tok {t['predicted_per_second']} tok/s\n")
         self._emit(req, "done", reason)
         s.state, s.req, s.t_last_used = SlotState.IDLE, None, time.time()
+        self._drop_drafter(s)
         if not req.cache_prompt:
             self.eng.truncate_seq(s.sid, 0)
             s.cache_tokens, s.n_past = [], 0
@@ -451,7 +473,16 @@ class Scheduler:
         except Exception:
             pass
         s.state, s.req, s.cache_tokens, s.n_past = SlotState.IDLE, None, [], 0
+        self._drop_drafter(s)
         req.done.set()
+
+    def _drop_drafter(self, s: Slot):
+        d = self._drafters.pop(s.idx, None)
+        if d is not None:
+            try:
+                d.close()
+            except Exception:
+                pass
 
     # ---- background loop --------------------------------------------------------------------------------
     def start(self):

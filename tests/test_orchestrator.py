@@ -331,3 +331,43 @@ def test_scheduler_speculative_lookup_matches_plain_greedy(tmp_models):
         t.join()
     sched.stop()
     assert out["a"].output_ids == plain.output_ids[:16] and len(out["b"].output_ids) == 16
+
+
+def test_scheduler_draft_model_speculation(tmp_models):
+    """`-md`: a draft engine proposes blocks, the target verifies them in one forward - identical greedy text, fewer target
+    passes; a quantised copy of the model drafts (high but not total agreement), slots keep separate draft sequences."""
+    target, draft = tmp_models[("tiny", "F16")], tmp_models[("tiny", "Q8_0")]
+    plain_s, _, _ = build_service(target, device="cpu", n_ctx=256, n_slots=2, n_batch=64)
+    prompt = "one two three four five"
+    plain = plain_s.generate(prompt, n_predict=32, sampling=SamplingParams(temperature=0.0), cache_prompt=False, ignore_eos=True)
+    n_plain = plain_s.metrics.c["n_decode_total"]
+    sched, info, logs = build_service(target, device="cpu", n_ctx=256, n_slots=2, n_batch=64, model_draft=draft, draft_max=6)
+    assert info["draft_model"].endswith("Q8_0.gguf") and any("draft model" in l for l in logs)
+    spec = sched.generate(prompt, n_predict=32, sampling=SamplingParams(temperature=0.0), cache_prompt=False, ignore_eos=True)
+    assert spec.output_ids == plain.output_ids and spec.text == plain.text
+    c = sched.metrics.c
+    assert c["draft_tokens_total"] > 0 and c["draft_tokens_accepted_total"] > 0.5 * c["draft_tokens_total"]
+    assert c["n_decode_total"] < n_plain
+    assert not sched._drafters and not sched.draft_eng.seqs             # the draft sequence was released with the request
+    # a sampled request is not speculated; n_draft < 0 switches it off for one greedy request
+    before = c["draft_tokens_total"]
+    sched.generate(prompt, n_predict=8, sampling=SamplingParams(temperature=0.8, seed=1), ignore_eos=True)
+    off = sched.generate(prompt, n_predict=8, sampling=SamplingParams(temperature=0.0), ignore_eos=True, cache_prompt=False, n_draft=-1)
+    assert sched.metrics.c["draft_tokens_total"] == before and off.output_ids == plain.output_ids[:8]
+    # two greedy requests at once: one draft sequence each
+    import threading
+    out = {}
+    ts = [threading.Thread(target=lambda k=k, p=p: out.__setitem__(k, sched.generate(p, n_predict=16, sampling=SamplingParams(temperature=0.0), ignore_eos=True, cache_prompt=False)))
+          for k, p in (("a", prompt), ("b", "six seven eight"))]
+    sched.start()
+    for t in ts:
+        t.start()
+    for t in ts:
+        t.join()
+    sched.stop()
+    assert out["a"].output_ids == plain.output_ids[:16]
+    ref_b = plain_s.generate("six seven eight", n_predict=16, sampling=SamplingParams(temperature=0.0), ignore_eos=True, cache_prompt=False)
+    assert out["b"].output_ids == ref_b.output_ids
+    # a draft model with another vocabulary is refused
+    with pytest.raises(ValueError):
+        build_service(target, device="cpu", n_ctx=64, n_slots=1, n_batch=32, model_draft=tmp_models[("tiny128", "F16")])

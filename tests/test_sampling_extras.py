@@ -159,3 +159,41 @@ def test_mirostat_v1_and_jinja_chat_template():
     # a template that raises falls back to the marker-based formats
     bad = "{% for m in messages %}{{ raise_exception('no') }}{% endfor %}<|im_start|>"
     assert apply_chat_template({"tokenizer.chat_template": bad}, msgs).endswith("<|im_start|>assistant\n")
+
+
+def test_infill_sampler_rules():
+    """`llama_sampler_init_infill` behaviour on hand-made distributions."""
+    import math
+    from distributed_llm_pipeline_b200.serving.sampler import apply_infill
+    pieces = ["<eos>", "foo", "foobar", "fo", "zed", "qux", "<eot>", "x"]
+    eog, eot = {0, 6}, 6
+
+    def lp(probs):
+        return torch.log(torch.tensor(probs))
+
+    def alive(out):
+        return {i: math.exp(v) for i, v in enumerate(out.tolist()) if v != float("-inf")}
+
+    # 1. end-of-generation mass matters (3 * p_eog * n > p_txt): only EOG tokens survive, renormalised
+    out = alive(apply_infill(lp([0.05, 0.3, 0.2, 0.1, 0.2, 0.1, 0.05, 0.0001]), pieces, eog, eot))
+    assert set(out) == {0, 6} and abs(out[0] - 0.5) < 1e-4
+    # 2. "fo" / "foo" / "foobar" are one continuation: merged into the likeliest ("foo"), which then clears the thresholds
+    out = alive(apply_infill(lp([1e-9, 0.35, 0.25, 0.15, 0.15, 0.1 - 2e-9, 1e-9, 1e-9]), pieces, eog, eot))
+    text = {i: v for i, v in out.items() if i not in eog}
+    assert set(text) == {1} and sum(out.values()) == pytest.approx(1.0, abs=1e-4) and text[1] > 0.99
+    # 3. nothing confident: every text token is below 0.2 after merging -> the end-of-turn token is forced
+    flat = apply_infill(lp([1e-9, 0.15, 1e-9, 1e-9, 0.15, 0.15, 1e-9, 0.15] + [0.1] * 4), pieces + ["a1", "b2", "c3", "d4"], eog, eot)
+    assert alive(flat) == {6: 1.0}
+    # through the Sampler: a request flagged infill takes the host path and ends when unsure
+    from distributed_llm_pipeline_b200.serving.sampler import Sampler, SamplingParams
+
+    class Tok:
+        eot_id, eos_id, stop_ids = 6, 0, {0, 6}
+
+        def token_texts(self):
+            return pieces
+    sp = SamplingParams(temperature=0.0, infill=True)
+    assert sp.host_only
+    s = Sampler(sp, Tok())
+    assert s.sample(lp([0.05, 0.3, 0.2, 0.1, 0.2, 0.1, 0.05, 0.0001])) in (0, 6)
+    assert s.sample(lp([1e-9, 0.35, 0.25, 0.15, 0.15, 0.1 - 2e-9, 1e-9, 1e-9])) == 1
