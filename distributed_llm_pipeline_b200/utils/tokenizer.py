@@ -55,7 +55,24 @@ class Tokenizer:
         self.add_space_prefix = bool(meta.get("tokenizer.ggml.add_space_prefix", True))
         self.tok2id = {t: i for i, t in enumerate(self.tokens)}
         self.byte_ids: dict[int, int] = {}
-        if self.model == "llama":
+        self.codec = None       # WordPiece / Unigram / RWKV vocabularies (utils/tokenizer_extra.py)
+        self.add_eos = bool(meta.get("tokenizer.ggml.add_eos_token", self.model in ("bert", "t5")))
+        if self.model in ("bert", "t5", "rwkv"):
+            from .tokenizer_extra import RwkvCodec, UgmCodec, WpmCodec
+            if self.model == "bert":
+                self.codec = WpmCodec(self.tokens, self.unk_id)
+                self.bos_id = int(meta.get("tokenizer.ggml.cls_token_id", meta.get("tokenizer.ggml.bos_token_id", 101)))
+                self.add_bos = bool(meta.get("tokenizer.ggml.add_bos_token", True))      # [CLS] ... [SEP]
+                self.sep_id = int(meta.get("tokenizer.ggml.seperator_token_id", meta.get("tokenizer.ggml.eos_token_id", self.eos_id)))
+            elif self.model == "t5":
+                self.codec = UgmCodec(self.tokens, self.scores, self.types, self.unk_id, self.add_space_prefix,
+                                      bool(meta.get("tokenizer.ggml.remove_extra_whitespaces", True)))
+                self.add_bos = bool(meta.get("tokenizer.ggml.add_bos_token", False))
+            else:
+                self.codec = RwkvCodec(self.tokens, self.unk_id)
+                self.add_bos = bool(meta.get("tokenizer.ggml.add_bos_token", False))
+                self.add_eos = bool(meta.get("tokenizer.ggml.add_eos_token", False))
+        elif self.model == "llama":
             for b in range(256):
                 tid = self.tok2id.get(f"<0x{b:02X}>")
                 if tid is not None:
@@ -139,6 +156,8 @@ class Tokenizer:
         return parts
 
     def _encode_plain(self, text: str) -> list[int]:
+        if self.codec is not None:
+            return self.codec.encode(text)
         if self.model == "llama":
             t = text.replace(" ", SPM_SPACE)
             return self._spm_encode(t)
@@ -177,6 +196,8 @@ class Tokenizer:
                     seg = " " + seg
                 ids.extend(self._encode_plain(seg))
             first = False
+        if getattr(self, "add_eos", False) and (add_bos if add_bos is not None else True):
+            ids.append(getattr(self, "sep_id", self.eos_id))          # bert: [SEP], t5: </s>
         return ids
 
     # ---- decode -----------------------------------------------------------------------------------
@@ -184,6 +205,8 @@ class Tokenizer:
         if tid < 0 or tid >= self.n_vocab:
             return b""
         t, typ = self.tokens[tid], self.types[tid]
+        if self.codec is not None:
+            return self.codec.token_bytes(tid, typ)
         if typ == TokenType.CONTROL:
             return b""
         if self.model == "llama":
@@ -224,7 +247,7 @@ class Tokenizer:
     def decode(self, ids: list[int], strip_leading_space: bool = True) -> str:
         data = b"".join(self.token_bytes(i) for i in ids)
         s = data.decode("utf-8", errors="replace")
-        if self.model == "llama" and strip_leading_space and self.add_space_prefix and s.startswith(" "):
+        if self.model in ("llama", "bert", "t5") and strip_leading_space and self.add_space_prefix and s.startswith(" "):
             s = s[1:]
         return s
 
