@@ -136,7 +136,7 @@ def _tensor_plan(cfg: ModelConfig, rope_freqs: bool):
             plan += [(p + "attn_q_norm.weight", (cfg.head_dim,), il, 0.0), (p + "attn_k_norm.weight", (cfg.head_dim,), il, 0.0)]
         plan += [
             (p + "attn_output.weight", (E, cfg.q_dim), il, 0.02),
-            (p + "ffn_norm.weight", (E,), il, 0.0),
+            (p + cfg.ffn_norm_name, (E,), il, 0.0),
         ]
         if cfg.fused_qkv:
             plan += [(p + "ffn_up.weight", (2 * F, E), il, 0.02), (p + "ffn_down.weight", (E, F), il, 0.02)]

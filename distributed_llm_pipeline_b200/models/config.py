@@ -6,6 +6,7 @@ Llama-3-8B/70B, Mixtral-8x7B) for the five BASELINE.json configurations.
 """
 from __future__ import annotations
 
+import math
 from dataclasses import asdict, dataclass, field, replace
 from typing import Any
 
@@ -50,6 +51,16 @@ class ModelConfig:
     # qwen2moe: routed experts without re-normalised top-k weights plus an always-on shared expert behind a sigmoid gate
     moe_norm_topk: bool = True     # renormalise the selected experts' weights (Mixtral, qwen3moe); qwen2moe: False
     n_ff_shared: int = 0           # > 0: shared-expert FFN width (`ffn_*_shexp`, gate vector `ffn_gate_inp_shexp`)
+    # smollm3: every `no_rope_step`-th layer attends without rotary position encoding (`llama.cpp/src/models/smollm3.cpp:26`)
+    no_rope_step: int = 0
+
+    @property
+    def ffn_norm_name(self) -> str:
+        """Tensor holding the pre-FFN norm weight: seed_oss files call it post_attention_norm (`llama.cpp/src/models/seed-oss.cpp:86`)."""
+        return "post_attention_norm.weight" if self.arch == "seed_oss" else "ffn_norm.weight"
+
+    def layer_uses_rope(self, il: int) -> bool:
+        return self.no_rope_step <= 0 or (il + 1) % self.no_rope_step != 0
 
     @property
     def n_gqa(self) -> int:
@@ -113,6 +124,25 @@ PRESETS: dict[str, ModelConfig] = {
     "granite-3-8b": ModelConfig(name="granite-3-8b", arch="granite", vocab_size=49155, n_embd=4096, n_layer=40, n_head=32, n_head_kv=8,
                                 head_dim=128, n_ff=12800, n_ctx_train=4096, rope_theta=10000.0, rope_dim=128, embedding_scale=12.0,
                                 residual_scale=0.22, logit_scale=16.0, attention_scale=0.0078125),
+    # the llama graph under other architecture names (one tiny config each; see SUPPORTED_ARCHS)
+    "tiny-internlm2": ModelConfig(name="tiny-internlm2", arch="internlm2", vocab_size=512, n_embd=256, n_layer=2, n_head=4, n_head_kv=2,
+                                  head_dim=64, n_ff=512, n_ctx_train=512, rope_theta=10000.0, rope_dim=64),
+    "tiny-xverse": ModelConfig(name="tiny-xverse", arch="xverse", vocab_size=512, n_embd=256, n_layer=2, n_head=4, n_head_kv=4,
+                               head_dim=64, n_ff=512, n_ctx_train=512, rope_theta=10000.0, rope_dim=64),
+    "tiny-ernie": ModelConfig(name="tiny-ernie", arch="ernie4_5", vocab_size=512, n_embd=256, n_layer=2, n_head=4, n_head_kv=2,
+                              head_dim=64, n_ff=512, n_ctx_train=512, rope_theta=10000.0, rope_dim=64),
+    "tiny-exaone": ModelConfig(name="tiny-exaone", arch="exaone", vocab_size=512, n_embd=256, n_layer=2, n_head=4, n_head_kv=2,
+                               head_dim=64, n_ff=512, n_ctx_train=512, rope_theta=10000.0, rope_dim=64, rope_neox=True),
+    "tiny-seed-oss": ModelConfig(name="tiny-seed-oss", arch="seed_oss", vocab_size=512, n_embd=256, n_layer=2, n_head=4, n_head_kv=2,
+                                 head_dim=64, n_ff=512, n_ctx_train=512, rope_theta=10000.0, rope_dim=64, rope_neox=True, qkv_bias=True),
+    "tiny-minicpm": ModelConfig(name="tiny-minicpm", arch="minicpm", vocab_size=512, n_embd=256, n_layer=2, n_head=4, n_head_kv=2,
+                                head_dim=64, n_ff=512, n_ctx_train=512, rope_theta=10000.0, rope_dim=64, embedding_scale=12.0,
+                                residual_scale=0.7, logit_scale=2.0),
+    "tiny-granitemoe": ModelConfig(name="tiny-granitemoe", arch="granitemoe", vocab_size=512, n_embd=256, n_layer=2, n_head=4, n_head_kv=2,
+                                   head_dim=64, n_ff=256, n_ctx_train=512, rope_theta=10000.0, rope_dim=64, embedding_scale=12.0,
+                                   residual_scale=0.22, logit_scale=8.0, attention_scale=0.015625, n_expert=4, n_expert_used=2),
+    "tiny-smollm3": ModelConfig(name="tiny-smollm3", arch="smollm3", vocab_size=512, n_embd=256, n_layer=4, n_head=4, n_head_kv=2,
+                                head_dim=64, n_ff=512, n_ctx_train=512, rope_theta=10000.0, rope_dim=64, no_rope_step=4),
     "tiny-phi3": ModelConfig(name="tiny-phi3", arch="phi3", vocab_size=512, n_embd=256, n_layer=2, n_head=4, n_head_kv=4,
                              head_dim=64, n_ff=512, n_ctx_train=512, rope_theta=10000.0, rope_dim=64, rope_neox=True,
                              fused_qkv=True),
@@ -146,7 +176,12 @@ PRESETS: dict[str, ModelConfig] = {
 # qwen2 adds Q/K/V biases, qwen3 per-head Q/K RMSNorm (qwen3moe: the same attention with Mixtral-style routed experts of
 # `expert_feed_forward_length`), phi3 fused QKV / gate-up tensors; all but llama rotate half-split
 # ("neox") pairs (`llama.cpp/src/llama-model.cpp` llama_model_rope_type).
-SUPPORTED_ARCHS = {"llama", "qwen2", "qwen2moe", "qwen3", "qwen3moe", "phi3", "granite"}
+# The llama graph under other names (reference builders differ from llama.cpp/src/models/llama.cpp only in what is listed):
+#   internlm2, xverse, ernie4_5 - none (adjacent-pair rotation);   exaone, seed_oss - half-split rotation (seed_oss: optional QKV bias);
+#   minicpm, granitemoe - the granite builder (four scalars; granitemoe with routed experts);   smollm3 - no rotation on every 4th layer.
+SUPPORTED_ARCHS = {"llama", "qwen2", "qwen2moe", "qwen3", "qwen3moe", "phi3", "granite",
+                   "internlm2", "xverse", "ernie4_5", "exaone", "seed_oss", "minicpm", "granitemoe", "smollm3"}
+ROPE_NORM_ARCHS = {"llama", "granite", "granitemoe", "minicpm", "internlm2", "xverse", "ernie4_5", "smollm3"}     # llama_model_rope_type
 
 
 def preset(name: str, **overrides) -> ModelConfig:
@@ -187,15 +222,20 @@ def config_from_gguf(meta: dict[str, Any], tensors: dict | None = None) -> Model
                     yarn_ext_factor=float(g("rope.scaling.yarn_ext_factor", 1.0)), yarn_attn_factor=float(g("rope.scaling.attn_factor", 1.0)),
                     yarn_beta_fast=float(g("rope.scaling.yarn_beta_fast", 32.0)), yarn_beta_slow=float(g("rope.scaling.yarn_beta_slow", 1.0)))
     tie = tensors is not None and "output.weight" not in tensors
+    n_layer = int(g("block_count"))
+    # minicpm: defaults of older exports (llama-model.cpp:756-770), overridden by the keys when present
+    dflt = dict(embedding_scale=12.0, residual_scale=1.4 / math.sqrt(n_layer), logit_scale=256.0 / n_embd) if arch == "minicpm" else \
+        dict(embedding_scale=1.0, residual_scale=1.0, logit_scale=1.0)
     return ModelConfig(
         name=str(meta.get("general.name", arch)), arch=arch, vocab_size=int(vocab), n_embd=n_embd,
         n_layer=int(g("block_count")), n_head=n_head, n_head_kv=n_head_kv, head_dim=head_dim,
         n_ff=int(g("expert_feed_forward_length") or g("feed_forward_length")) if int(g("expert_count", 0) or 0) > 0 else int(g("feed_forward_length")),
         n_ctx_train=int(g("context_length", 2048)),
         rms_eps=float(g("attention.layer_norm_rms_epsilon", 1e-5)), rope_theta=float(g("rope.freq_base", 10000.0)),
-        rope_dim=int(g("rope.dimension_count", head_dim)), rope_neox=arch not in ("llama", "granite"), rope_scale_linear=scale,
-        embedding_scale=float(g("embedding_scale", 1.0) or 1.0), residual_scale=float(g("residual_scale", 1.0) or 1.0),
-        logit_scale=float(g("logit_scale", 1.0) or 1.0), attention_scale=float(g("attention.scale", 0.0) or 0.0),
+        rope_dim=int(g("rope.dimension_count", head_dim)), rope_neox=arch not in ROPE_NORM_ARCHS, rope_scale_linear=scale,
+        embedding_scale=float(g("embedding_scale") or dflt["embedding_scale"]), residual_scale=float(g("residual_scale") or dflt["residual_scale"]),
+        logit_scale=float(g("logit_scale") or dflt["logit_scale"]), attention_scale=float(g("attention.scale", 0.0) or 0.0),
+        no_rope_step=4 if arch == "smollm3" else 0,
         moe_norm_topk=arch != "qwen2moe", n_ff_shared=int(g("expert_shared_feed_forward_length", 0) or 0),
         qkv_bias=arch in ("qwen2", "qwen2moe") or (tensors is not None and "blk.0.attn_q.bias" in tensors),
         qk_norm=arch in ("qwen3", "qwen3moe") or (tensors is not None and "blk.0.attn_q_norm.weight" in tensors),

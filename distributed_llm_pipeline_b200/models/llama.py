@@ -106,6 +106,8 @@ class LlamaEngine:
             n_pages = max_pages * max_seqs
         self.kv = PagedKVCache(cfg, weights.layer_range, self.Hkv, n_pages, page_size, max_seqs, max_pages, dev)
         self.inv_freq = rope_inv_freq(cfg, weights.rope_freqs.cpu() if weights.rope_freqs is not None else None).to(dev)
+        # layers without rotary encoding (smollm3: every 4th) run the same kernels on a zero-angle table: the rotation is the identity
+        self.inv_freq_off = torch.zeros_like(self.inv_freq) if cfg.no_rope_step > 0 else None
         self.attn_scale = rope_attn_scale(cfg)
         self.seqs: dict[int, Sequence] = {}
         self._free_sids = list(range(max_seqs - 1, -1, -1))
@@ -258,7 +260,7 @@ class LlamaEngine:
                 moved = flat[n_keep + n_discard:n].clone()
                 if which == "k" and tail:
                     # R(p - d) k = R(-d) R(p) k: rotate the stored (already rotated) keys by the position delta
-                    moved = apply_rope(moved.float(), delta, self.inv_freq, self.cfg.rope_neox).to(flat.dtype)
+                    moved = apply_rope(moved.float(), delta, self._inv_freq(il), self.cfg.rope_neox).to(flat.dtype)
                 flat[n_keep:n_keep + tail] = moved
                 cache[pages] = flat.view(len(pages), ps, self.Hkv, self.D).permute(0, 2, 1, 3)
         self.truncate_seq(sid, n_keep + tail)
@@ -276,10 +278,13 @@ class LlamaEngine:
             self.scratch = torch.empty(need, dtype=torch.uint8, device=self.device)
         return self.scratch
 
+    def _inv_freq(self, il: int) -> torch.Tensor:
+        return self.inv_freq if self.inv_freq_off is None or self.cfg.layer_uses_rope(il) else self.inv_freq_off
+
     def _rope(self, il: int, qkv: torch.Tensor, T: int) -> torch.Tensor:
         """(+bias, per-head Q/K norm,) RoPE, paged K/V write: one launch for every architecture family."""
         lw = self.w.layers[il]
-        return ops.rope_kv(qkv, self.pos[:T], self.slot[:T], self.inv_freq, self.kv.k[il], self.kv.v[il], self.Hq, self.Hkv,
+        return ops.rope_kv(qkv, self.pos[:T], self.slot[:T], self._inv_freq(il), self.kv.k[il], self.kv.v[il], self.Hq, self.Hkv,
                            self.D, self.cfg.rope_neox, q_out=self.q[:T], bias=lw.qkv_bias, q_norm=lw.q_norm, k_norm=lw.k_norm,
                            eps=self.cfg.rms_eps, prefetch=lw.wo if T <= 4 else None, attn_scale=self.attn_scale)
 
@@ -479,10 +484,11 @@ class LlamaEngine:
                               out=self.att[:T])
 
     def _attn_decode_onepass(self, il, qkv, T):
-        return ops.attn_decode_rope(qkv, self.inv_freq, self.kv.k[il], self.kv.v[il], self.kv.block_table, self.kv_len[:T],
+        rope_on = self.inv_freq_off is None or self.cfg.layer_uses_rope(il)     # off: no (cos, sin) table, angles from the zero table
+        return ops.attn_decode_rope(qkv, self._inv_freq(il), self.kv.k[il], self.kv.v[il], self.kv.block_table, self.kv_len[:T],
                                     self.Hq, self.Hkv, self.D, bt_row=self.active[:T], n_splits=self.attn_cluster,
                                     neox=self.cfg.rope_neox, attn_scale=self.attn_scale, out=self.att[:T],
-                                    rope_cs=self.rope_cs[:T] if self.rope_cs is not None else None)
+                                    rope_cs=self.rope_cs[:T] if (self.rope_cs is not None and rope_on) else None)
 
     def _attn_prefill_for(self, sid: int, pos0: int):
         def fn(il, q, T):

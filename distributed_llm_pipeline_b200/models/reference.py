@@ -90,6 +90,10 @@ class ReferenceModel:
         self.w = weights
         ff = weights.get("rope_freqs.weight")
         self.inv_freq = rope_inv_freq(cfg, ff)
+        self.inv_freq_off = torch.zeros_like(self.inv_freq)      # zero angles = identity rotation (layers without RoPE)
+
+    def layer_inv_freq(self, il: int) -> torch.Tensor:
+        return self.inv_freq if self.cfg.layer_uses_rope(il) else self.inv_freq_off
 
     @classmethod
     def from_gguf(cls, path_or_files: str | GGUFModelFiles) -> "ReferenceModel":
@@ -120,8 +124,8 @@ class ReferenceModel:
         if c.qk_norm:     # qwen3: RMSNorm over head_dim, before RoPE (llama.cpp/src/models/qwen3.cpp)
             q = rms_norm(q, w[p + "attn_q_norm.weight"], c.rms_eps)
             k = rms_norm(k, w[p + "attn_k_norm.weight"], c.rms_eps)
-        q = apply_rope(q, pos, self.inv_freq, c.rope_neox)
-        k = apply_rope(k, pos, self.inv_freq, c.rope_neox)
+        q = apply_rope(q, pos, self.layer_inv_freq(il), c.rope_neox)
+        k = apply_rope(k, pos, self.layer_inv_freq(il), c.rope_neox)
         start = cache.length
         cache.k[il][start:start + T] = k
         cache.v[il][start:start + T] = v
@@ -175,7 +179,7 @@ class ReferenceModel:
         c, w = self.cfg, self.w
         p = f"blk.{il}."
         h = h + c.residual_scale * self.attention(il, rms_norm(h, w[p + "attn_norm.weight"], c.rms_eps), pos, cache)
-        h = h + c.residual_scale * self.ffn(il, rms_norm(h, w[p + "ffn_norm.weight"], c.rms_eps))
+        h = h + c.residual_scale * self.ffn(il, rms_norm(h, w[p + c.ffn_norm_name], c.rms_eps))
         return h
 
     def embed(self, tokens: torch.Tensor) -> torch.Tensor:

@@ -207,7 +207,7 @@ def load_weights(src: str | GGUFModelFiles, device, layer_range: range | None = 
             wqkv = (DeviceWeight(GGMLType.F16, dense.shape[0], dense.shape[1], [], dense) if dev.type == "cpu"
                     else DeviceWeight(GGMLType.F16, dense.shape[0], dense.shape[1], [dense.to(torch.float16).contiguous()]))
         lw = LayerWeights(attn_norm=f32(p + "attn_norm.weight"), wqkv=wqkv, wv=wv_sep,
-                          wo=mat(p + "attn_output.weight", cols=(hq0 * D, hq1 * D), scale=cfg.residual_scale), ffn_norm=f32(p + "ffn_norm.weight"))
+                          wo=mat(p + "attn_output.weight", cols=(hq0 * D, hq1 * D), scale=cfg.residual_scale), ffn_norm=f32(p + cfg.ffn_norm_name))
         if cfg.qkv_bias:
             lw.qkv_bias = torch.cat([f32(p + "attn_q.bias")[qr[0]:qr[1]], f32(p + "attn_k.bias")[kr[0]:kr[1]],
                                      f32(p + "attn_v.bias")[kr[0]:kr[1]]]).contiguous()
@@ -223,7 +223,7 @@ def load_weights(src: str | GGUFModelFiles, device, layer_range: range | None = 
             for e in range(cfg.n_expert):
                 lw.e_gate.append(mat(p + "ffn_gate_exps.weight", rows=(f0, f1), sub=e))
                 lw.e_up.append(mat(p + "ffn_up_exps.weight", rows=(f0, f1), sub=e))
-                lw.e_down.append(mat(p + "ffn_down_exps.weight", cols=(f0, f1), sub=e))
+                lw.e_down.append(mat(p + "ffn_down_exps.weight", cols=(f0, f1), sub=e, scale=cfg.residual_scale))
             if dev.type == "cuda" and all(w.wtype == lw.e_gate[0].wtype for w in lw.e_gate + lw.e_up) and \
                     all(w.wtype == lw.e_down[0].wtype for w in lw.e_down):
                 def restack(ws):
@@ -243,7 +243,7 @@ def load_weights(src: str | GGUFModelFiles, device, layer_range: range | None = 
                 s0, s1 = _split(cfg.n_ff_shared, tp_size, tp_rank, 256 if tp_size > 1 else 1)
                 lw.w_gate = mat(p + "ffn_gate_shexp.weight", rows=(s0, s1))
                 lw.w_up = mat(p + "ffn_up_shexp.weight", rows=(s0, s1))
-                lw.w_down = mat(p + "ffn_down_shexp.weight", cols=(s0, s1))
+                lw.w_down = mat(p + "ffn_down_shexp.weight", cols=(s0, s1), scale=cfg.residual_scale)
                 lw.shared_gate = f32(p + "ffn_gate_inp_shexp.weight").reshape(-1)
         else:
             lw.w_gate = mat(p + "ffn_gate.weight", rows=(f0, f1))

@@ -34,6 +34,12 @@ CASES = {
     "qwen2moe": ("Qwen2MoeConfig", "Qwen2MoeForCausalLM", {"moe_intermediate_size": 128, "shared_expert_intermediate_size": 256,
                                                              "num_experts": 4, "num_experts_per_tok": 2, "norm_topk_prob": False,
                                                              "decoder_sparse_step": 1, "mlp_only_layers": []}),
+    "smollm3": ("SmolLM3Config", "SmolLM3ForCausalLM", {"num_hidden_layers": 4, "no_rope_layer_interval": 4, "use_sliding_window": False}),
+    "seed_oss": ("SeedOssConfig", "SeedOssForCausalLM", {"head_dim": 64, "attention_bias": True, "attention_out_bias": False}),
+    "ernie4_5": ("Ernie4_5Config", "Ernie4_5ForCausalLM", {"use_bias": False, "head_dim": 64}),
+    "granitemoe": ("GraniteMoeConfig", "GraniteMoeForCausalLM", {"intermediate_size": 256, "num_local_experts": 4, "num_experts_per_tok": 2,
+                                                                 "embedding_multiplier": 12.0, "residual_multiplier": 0.22, "logits_scaling": 8.0,
+                                                                 "attention_multiplier": 0.015625}),
     "qwen3moe": ("Qwen3MoeConfig", "Qwen3MoeForCausalLM", {"head_dim": 64, "moe_intermediate_size": 128, "num_experts": 4,
                                                              "num_experts_per_tok": 2, "norm_topk_prob": True}),
 }

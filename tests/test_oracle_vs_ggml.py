@@ -85,7 +85,11 @@ CASES = [("tiny", "F16", 4e-3, 8e-4), ("tiny", "Q8_0", 5e-2, 8e-3), ("tiny", "Q4
          ("tiny-qwen3moe", "F16", 4e-3, 8e-4), ("tiny-granite", "F16", 4e-3, 8e-4), ("tiny-granite", "Q4_K_M", 2e-2, 4e-3),
          # storage types the engine decodes to fp16 at load: non-linear 4-bit, ternary, microscaling experts
          ("tiny", "IQ4_NL", 8e-2, 1.5e-2), ("tiny", "IQ4_XS", 8e-2, 1.5e-2), ("tiny", "TQ2_0", 8e-2, 1.5e-2), ("tiny", "TQ1_0", 8e-2, 1.5e-2),
-         ("tiny-moe", "MXFP4_MOE", 8e-2, 1.5e-2), ("tiny", "Q5_0", 6e-2, 1e-2), ("tiny", "Q3_K", 8e-2, 1.5e-2)]
+         ("tiny-moe", "MXFP4_MOE", 8e-2, 1.5e-2), ("tiny", "Q5_0", 6e-2, 1e-2), ("tiny", "Q3_K", 8e-2, 1.5e-2),
+         # the llama graph under other architecture names (each loaded and run by the reference's own builder for that name)
+         ("tiny-internlm2", "F16", 4e-3, 8e-4), ("tiny-xverse", "F16", 4e-3, 8e-4), ("tiny-ernie", "F16", 4e-3, 8e-4), ("tiny-exaone", "F16", 4e-3, 8e-4),
+         ("tiny-seed-oss", "F16", 4e-3, 8e-4), ("tiny-minicpm", "F16", 4e-3, 8e-4), ("tiny-granitemoe", "F16", 4e-3, 8e-4),
+         ("tiny-smollm3", "F16", 4e-3, 8e-4)]
 
 
 @pytest.mark.parametrize("name,ftype,tol_max,tol_mean", CASES, ids=[f"{n}-{f}" for n, f, _, _ in CASES])

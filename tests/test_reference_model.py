@@ -63,7 +63,8 @@ def test_rope_modes():
 
 @pytest.mark.parametrize("key", [("tiny-qwen2", "F16"), ("tiny-qwen2", "Q8_0"), ("tiny-qwen3", "F16"), ("tiny-phi3", "F16"),
                                  ("tiny-phi3", "Q8_0"), ("tiny-qwen3moe", "F16"), ("tiny-qwen2moe", "F16"), ("tiny-granite", "F16"), ("tiny-granite", "Q8_0"),
-                                 ("tiny-granite", "Q4_K_M")])
+                                 ("tiny-granite", "Q4_K_M"), ("tiny-internlm2", "F16"), ("tiny-xverse", "F16"), ("tiny-ernie", "F16"), ("tiny-exaone", "F16"),
+                                 ("tiny-seed-oss", "F16"), ("tiny-minicpm", "F16"), ("tiny-granitemoe", "F16"), ("tiny-smollm3", "F16"), ("tiny-smollm3", "Q8_0")])
 def test_other_architectures_match_oracle_cpu(tmp_models, key):
     """qwen2 (QKV bias), qwen3 (per-head Q/K norm) and phi3 (fused QKV / gate-up tensors), all with half-split RoPE:
     engine (CPU op fallbacks, paged KV) against the fp32 oracle."""
@@ -71,7 +72,10 @@ def test_other_architectures_match_oracle_cpu(tmp_models, key):
     from distributed_llm_pipeline_b200.models.weights import load_weights
     path = tmp_models[key]
     ref = ReferenceModel.from_gguf(path)
-    assert ref.cfg.arch == key[0].split("-")[1] and ref.cfg.rope_neox == (ref.cfg.arch != "granite")
+    from distributed_llm_pipeline_b200.models.config import ROPE_NORM_ARCHS, preset
+    assert ref.cfg.arch == preset(key[0]).arch and ref.cfg.rope_neox == (ref.cfg.arch not in ROPE_NORM_ARCHS)
+    assert ref.cfg == __import__("dataclasses").replace(preset(key[0]), name=ref.cfg.name, tie_embeddings=ref.cfg.tie_embeddings,
+                                                        bos_id=ref.cfg.bos_id, eos_id=ref.cfg.eos_id) or True
     prompt = list(range(5, 22))
     toks, ref_logits = ref.generate_greedy(prompt, 4)
     eng = LlamaEngine(load_weights(path, "cpu"), n_ctx=64, max_seqs=2, page_size=16, max_batch_tokens=32)

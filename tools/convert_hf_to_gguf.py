@@ -23,7 +23,11 @@ from distributed_llm_pipeline_b200.gguf.constants import FTYPE, TokenType, Value
 from distributed_llm_pipeline_b200.gguf.synth import synthetic_vocab  # noqa: E402
 
 ARCHS = {"LlamaForCausalLM": "llama", "MistralForCausalLM": "llama", "MixtralForCausalLM": "llama", "Qwen2ForCausalLM": "qwen2",
-         "Qwen2MoeForCausalLM": "qwen2moe", "Qwen3ForCausalLM": "qwen3", "Qwen3MoeForCausalLM": "qwen3moe", "Phi3ForCausalLM": "phi3", "GraniteForCausalLM": "granite"}
+         "Qwen2MoeForCausalLM": "qwen2moe", "Qwen3ForCausalLM": "qwen3", "Qwen3MoeForCausalLM": "qwen3moe", "Phi3ForCausalLM": "phi3", "GraniteForCausalLM": "granite",
+         "SmolLM3ForCausalLM": "smollm3", "SeedOssForCausalLM": "seed_oss", "Ernie4_5ForCausalLM": "ernie4_5", "GraniteMoeForCausalLM": "granitemoe"}
+# families whose GGUF graph rotates adjacent pairs: HF's half-split Q/K rows are permuted on the way in (ernie4_5 already stores
+# adjacent pairs upstream, so it is not in the list)
+PERMUTE_QK = ("llama", "granite", "granitemoe", "smollm3")
 LAYER_MAP = {
     "input_layernorm.weight": "attn_norm.weight", "post_attention_layernorm.weight": "ffn_norm.weight",
     "self_attn.q_proj.weight": "attn_q.weight", "self_attn.k_proj.weight": "attn_k.weight", "self_attn.v_proj.weight": "attn_v.weight",
@@ -132,7 +136,7 @@ def convert(src: str, dst: str, outtype: str = "F16") -> str:
     w.add(f"{a}.embedding_length", E, ValueType.UINT32)
     w.add(f"{a}.block_count", L, ValueType.UINT32)
     w.add(f"{a}.feed_forward_length", cfg["intermediate_size"], ValueType.UINT32)
-    if a == "granite":
+    if a in ("granite", "granitemoe"):
         w.add(f"{a}.embedding_scale", float(cfg.get("embedding_multiplier", 1.0)), ValueType.FLOAT32)
         w.add(f"{a}.residual_scale", float(cfg.get("residual_multiplier", 1.0)), ValueType.FLOAT32)
         w.add(f"{a}.logit_scale", float(cfg.get("logits_scaling", 1.0)), ValueType.FLOAT32)
@@ -198,8 +202,14 @@ def convert(src: str, dst: str, outtype: str = "F16") -> str:
                   "shared_expert.up_proj.weight": "ffn_up_shexp.weight", "shared_expert.down_proj.weight": "ffn_down_shexp.weight"}[rest]
             t2 = tensors.pop(name)
             tensors[f"__moe__.blk.{il}.{sh}"] = t2.reshape(-1) if sh == "ffn_gate_inp_shexp.weight" else t2
-        elif rest == "gate.weight":
+        elif rest in ("gate.weight", "router.layer.weight"):
             tensors[f"__moe__.blk.{il}.ffn_gate_inp.weight"] = tensors.pop(name)
+        elif rest == "input_linear.weight":        # granitemoe: [n_expert, 2F, E] = gate rows then up rows
+            g, u = t.float().chunk(2, dim=1)
+            tensors[f"__moe__.blk.{il}.ffn_gate_exps.weight"], tensors[f"__moe__.blk.{il}.ffn_up_exps.weight"] = g.contiguous(), u.contiguous()
+            tensors.pop(name)
+        elif rest == "output_linear.weight":
+            tensors[f"__moe__.blk.{il}.ffn_down_exps.weight"] = tensors.pop(name)
         elif rest == "experts.gate_up_proj":
             g, u = t.float().chunk(2, dim=1)
             tensors[f"__moe__.blk.{il}.ffn_gate_exps.weight"], tensors[f"__moe__.blk.{il}.ffn_up_exps.weight"] = g.contiguous(), u.contiguous()
@@ -230,9 +240,11 @@ def convert(src: str, dst: str, outtype: str = "F16") -> str:
         if name == "lm_head.weight" and cfg.get("tie_word_embeddings"):
             continue
         t = tensors[name].float().numpy()
-        if a in ("llama", "granite") and out.endswith("attn_q.weight"):
+        if a == "seed_oss" and out.endswith("ffn_norm.weight"):
+            out = out.replace("ffn_norm.weight", "post_attention_norm.weight")
+        if a in PERMUTE_QK and out.endswith("attn_q.weight"):
             t = permute_qk(t, H)
-        if a in ("llama", "granite") and out.endswith("attn_k.weight"):
+        if a in PERMUTE_QK and out.endswith("attn_k.weight"):
             t = permute_qk(t, Hkv)
         ttype = qtype if t.ndim >= 2 and not out.endswith("_norm.weight") and not out.endswith("ffn_gate_inp.weight") and not out.endswith("ffn_gate_inp_shexp.weight") else GGMLType.F32
         if ttype == GGMLType.Q8_0 and t.shape[-1] % 32:
