@@ -468,6 +468,53 @@ def _kquant_affine_fit(x: np.ndarray, nmax: int):
     return scale, -mn
 
 
+def importance_weights(x: np.ndarray, imp: np.ndarray, block: int) -> np.ndarray:
+    """Per-element error weights from an importance matrix row (mean squared activation per input column):
+    w_j = imp_j * sqrt(sigma^2 + x_j^2) with sigma^2 = 2 * mean(x^2) over the block - the form the reference's weighted
+    encoders use (`quantize_row_q4_K_impl`, ggml-quants.c): columns that see large activations count more, and within a
+    block large weights count more than small ones."""
+    xb = x.reshape(-1, block)
+    sigma2 = 2.0 * (xb * xb).mean(axis=1, keepdims=True)
+    reps = xb.shape[0] // max(1, imp.size // block) if imp.size >= block else 1
+    cols = x.shape[-1]
+    imp_rows = np.broadcast_to(imp.reshape(1, cols), (x.size // cols, cols)).reshape(-1, block)
+    return (imp_rows * np.sqrt(sigma2 + xb * xb)).astype(np.float32)
+
+
+def _kquant_affine_fit_weighted(x: np.ndarray, w: np.ndarray, nmax: int, n_try: int = 9):
+    """Weighted version of `_kquant_affine_fit`: for a few shrunken ranges, round, then solve the weighted least-squares problem
+    min sum w (x - s q - b)^2 for (s, b <= 0) in closed form and keep the candidate with the smallest weighted error.
+    x, w: [nb, n_sub, sub].  Returns scale, minv (= -b) [nb, n_sub]."""
+    mn = np.minimum(x.min(axis=2), 0.0)
+    mx = x.max(axis=2)
+    rng = np.maximum(mx - mn, 1e-30)
+    best_s, best_m = rng / float(nmax), -mn
+    best_err = None
+    for k in range(n_try):
+        s0 = rng / (float(nmax) + 0.15 * k - 0.3)          # from slightly wider than the range to ~25 % tighter
+        q = np.clip(_nearest_int((x - mn[:, :, None]) / s0[:, :, None]), 0, nmax).astype(np.float32)
+        Sw, Sq, Sqq = w.sum(2), (w * q).sum(2), (w * q * q).sum(2)
+        Sx, Sxq = (w * x).sum(2), (w * x * q).sum(2)
+        det = Sw * Sqq - Sq * Sq
+        ok = det > 1e-30
+        s = np.where(ok, (Sw * Sxq - Sx * Sq) / np.where(ok, det, 1.0), s0)
+        b = np.where(ok, (Sqq * Sx - Sq * Sxq) / np.where(ok, det, 1.0), mn)
+        pos = b > 0                                          # the format stores a non-negative minimum: refit through the origin
+        s = np.where(pos, Sxq / np.maximum(Sqq, 1e-30), s)
+        b = np.where(pos, 0.0, b)
+        bad = ~(s > 0)
+        s, b = np.where(bad, s0, s), np.where(bad, mn, b)
+        q2 = np.clip(_nearest_int((x - b[:, :, None]) / s[:, :, None]), 0, nmax)
+        err = (w * (x - (s[:, :, None] * q2 + b[:, :, None])) ** 2).sum(2)
+        if best_err is None:
+            best_err, best_s, best_m = err, s, -b
+        else:
+            better = err < best_err
+            best_err = np.where(better, err, best_err)
+            best_s, best_m = np.where(better, s, best_s), np.where(better, -b, best_m)
+    return best_s.astype(np.float32), best_m.astype(np.float32)
+
+
 def _kquant_pack_super(scale: np.ndarray, minv: np.ndarray):
     """6-bit quantise sub-block scales/mins against fp16 super-scales d / dmin."""
     smax = scale.max(axis=1)
@@ -483,9 +530,9 @@ def _kquant_pack_super(scale: np.ndarray, minv: np.ndarray):
     return d, dmin, sc, mq
 
 
-def quant_q4_k(x: np.ndarray) -> np.ndarray:
+def quant_q4_k(x: np.ndarray, weights: np.ndarray | None = None) -> np.ndarray:
     x = np.ascontiguousarray(x, dtype=np.float32).reshape(-1, 8, 32)
-    scale, minv = _kquant_affine_fit(x, 15)
+    scale, minv = _kquant_affine_fit(x, 15) if weights is None else _kquant_affine_fit_weighted(x, weights.reshape(x.shape), 15)
     d, dmin, sc, mq = _kquant_pack_super(scale, minv)
     eff_s = d.astype(np.float32)[:, None] * sc
     eff_m = dmin.astype(np.float32)[:, None] * mq
@@ -500,9 +547,9 @@ def quant_q4_k(x: np.ndarray) -> np.ndarray:
     return out.reshape(-1)
 
 
-def quant_q5_k(x: np.ndarray) -> np.ndarray:
+def quant_q5_k(x: np.ndarray, weights: np.ndarray | None = None) -> np.ndarray:
     x = np.ascontiguousarray(x, dtype=np.float32).reshape(-1, 8, 32)
-    scale, minv = _kquant_affine_fit(x, 31)
+    scale, minv = _kquant_affine_fit(x, 31) if weights is None else _kquant_affine_fit_weighted(x, weights.reshape(x.shape), 31)
     d, dmin, sc, mq = _kquant_pack_super(scale, minv)
     eff_s = d.astype(np.float32)[:, None] * sc
     eff_m = dmin.astype(np.float32)[:, None] * mq
@@ -522,10 +569,30 @@ def quant_q5_k(x: np.ndarray) -> np.ndarray:
     return out.reshape(-1)
 
 
-def quant_q6_k(x: np.ndarray) -> np.ndarray:
+def _symmetric_scale_weighted(x: np.ndarray, w: np.ndarray, qmax: int, n_try: int = 9) -> np.ndarray:
+    """Weighted search for a symmetric scale: candidates around amax / qmax, each refined by s = sum(w x q) / sum(w q q)."""
+    amax = np.maximum(np.abs(x).max(axis=2), 1e-30)
+    best, best_err = amax / qmax, None
+    for k in range(n_try):
+        s0 = amax / (qmax + 0.2 * k - 0.4)
+        q = np.clip(_nearest_int(x / s0[:, :, None]), -qmax - 1, qmax).astype(np.float32)
+        den = (w * q * q).sum(2)
+        s = np.where(den > 0, (w * x * q).sum(2) / np.where(den > 0, den, 1.0), s0)
+        s = np.where(s > 0, s, s0)
+        q2 = np.clip(_nearest_int(x / s[:, :, None]), -qmax - 1, qmax)
+        err = (w * (x - s[:, :, None] * q2) ** 2).sum(2)
+        if best_err is None:
+            best, best_err = s, err
+        else:
+            better = err < best_err
+            best, best_err = np.where(better, s, best), np.where(better, err, best_err)
+    return best.astype(np.float32)
+
+
+def quant_q6_k(x: np.ndarray, weights: np.ndarray | None = None) -> np.ndarray:
     x = np.ascontiguousarray(x, dtype=np.float32).reshape(-1, 16, 16)  # 16 sub-blocks of 16
     amax = np.abs(x).max(axis=2)  # [nb, 16]
-    sub = amax / 31.0  # symmetric: q in [-31, 31]  (-32 never needed)
+    sub = amax / 31.0 if weights is None else _symmetric_scale_weighted(x, weights.reshape(x.shape), 31)  # symmetric: q in [-31, 31]
     smax = sub.max(axis=1)
     d = (smax / 127.0).astype(np.float16)
     df = d.astype(np.float32)
@@ -648,8 +715,12 @@ def quant_mxfp4(x: np.ndarray) -> np.ndarray:
 
 
 
-def quantize(x: np.ndarray, ggml_type: GGMLType) -> np.ndarray:
-    """Encode float32 data (last dim multiple of block size) -> raw uint8 bytes."""
+WEIGHTED_TYPES = (GGMLType.Q4_K, GGMLType.Q5_K, GGMLType.Q6_K)
+
+
+def quantize(x: np.ndarray, ggml_type: GGMLType, importance: np.ndarray | None = None) -> np.ndarray:
+    """Encode float32 data (last dim multiple of block size) -> raw uint8 bytes.  `importance` ([K], one value per input column,
+    e.g. a row of an imatrix file) switches the K-quant encoders to their error-weighted fits; other types ignore it."""
     t = GGMLType(ggml_type)
     x = np.ascontiguousarray(x, dtype=np.float32)
     if t == GGMLType.F32:
@@ -680,6 +751,12 @@ def quantize(x: np.ndarray, ggml_type: GGMLType) -> np.ndarray:
     }.get(t)
     if fn is None:
         raise NotImplementedError(f"quantize: unsupported type {t!r}")
+    if importance is not None and t in WEIGHTED_TYPES:
+        imp = np.maximum(np.asarray(importance, np.float32).reshape(-1), 0.0)
+        if imp.size != x.shape[-1]:
+            raise ValueError(f"importance has {imp.size} entries for rows of {x.shape[-1]}")
+        if float(imp.sum()) > 0:
+            return fn(x, importance_weights(x, imp, 256))
     return fn(x)
 
 

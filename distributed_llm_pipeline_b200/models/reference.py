@@ -92,6 +92,14 @@ class ReferenceModel:
         self.inv_freq = rope_inv_freq(cfg, ff)
         self.inv_freq_off = torch.zeros_like(self.inv_freq)      # zero angles = identity rotation (layers without RoPE)
 
+    observer = None     # fn(weight_name, x [T, K], expert | None): sees the input of every weight mat-mul (imatrix collection)
+
+    def mm(self, x: torch.Tensor, name: str, expert: int | None = None) -> torch.Tensor:
+        w = self.w[name] if expert is None else self.w[name][expert]
+        if self.observer is not None:
+            self.observer(name, x, expert)
+        return x @ w.T
+
     def layer_inv_freq(self, il: int) -> torch.Tensor:
         return self.inv_freq if self.cfg.layer_uses_rope(il) else self.inv_freq_off
 
@@ -113,9 +121,9 @@ class ReferenceModel:
         p = f"blk.{il}."
         T = x.shape[0]
         if c.fused_qkv:   # phi3: one [q | k | v] matrix (llama.cpp/src/models/phi3.cpp)
-            q, k, v = (x @ w[p + "attn_qkv.weight"].T).split([c.q_dim, c.kv_dim, c.kv_dim], dim=-1)
+            q, k, v = self.mm(x, p + "attn_qkv.weight").split([c.q_dim, c.kv_dim, c.kv_dim], dim=-1)
         else:
-            q, k, v = (x @ w[p + f"attn_{n}.weight"].T for n in "qkv")
+            q, k, v = (self.mm(x, p + f"attn_{n}.weight") for n in "qkv")
         if c.qkv_bias:    # qwen2 (llama.cpp/src/models/qwen2.cpp)
             q, k, v = (t + w[p + f"attn_{n}.bias"] for t, n in zip((q, k, v), "qkv"))
         q = q.reshape(T, c.n_head, c.head_dim)
@@ -139,18 +147,18 @@ class ReferenceModel:
         scores = scores.masked_fill(mask[None], float("-inf"))
         att = torch.softmax(scores, dim=-1)
         o = torch.einsum("hts,shd->thd", att, Vx).reshape(T, c.q_dim)
-        return o @ w[p + "attn_output.weight"].T
+        return self.mm(o, p + "attn_output.weight")
 
     def ffn(self, il: int, x: torch.Tensor) -> torch.Tensor:
         c, w = self.cfg, self.w
         p = f"blk.{il}."
         if c.fused_qkv:   # phi3: ffn_up holds [gate | up]; swiglu = silu(first half) * second half
-            g, u = (x @ w[p + "ffn_up.weight"].T).split([c.n_ff, c.n_ff], dim=-1)
-            return (torch.nn.functional.silu(g) * u) @ w[p + "ffn_down.weight"].T
+            g, u = self.mm(x, p + "ffn_up.weight").split([c.n_ff, c.n_ff], dim=-1)
+            return self.mm(torch.nn.functional.silu(g) * u, p + "ffn_down.weight")
         if not c.is_moe:
-            g = x @ w[p + "ffn_gate.weight"].T
-            u = x @ w[p + "ffn_up.weight"].T
-            return (torch.nn.functional.silu(g) * u) @ w[p + "ffn_down.weight"].T
+            g = self.mm(x, p + "ffn_gate.weight")
+            u = self.mm(x, p + "ffn_up.weight")
+            return self.mm(torch.nn.functional.silu(g) * u, p + "ffn_down.weight")
         logits = x @ w[p + "ffn_gate_inp.weight"].T
         probs = torch.softmax(logits, dim=-1)
         topw, topi = probs.topk(c.n_expert_used, dim=-1)
@@ -158,9 +166,9 @@ class ReferenceModel:
             topw = topw / topw.sum(-1, keepdim=True)
         out = torch.zeros_like(x)
         if c.n_ff_shared:   # qwen2moe: shared expert, scaled by sigmoid(x . gate_vector)  (llama.cpp/src/models/qwen2moe.cpp)
-            g = x @ w[p + "ffn_gate_shexp.weight"].T
-            u = x @ w[p + "ffn_up_shexp.weight"].T
-            sh = (torch.nn.functional.silu(g) * u) @ w[p + "ffn_down_shexp.weight"].T
+            g = self.mm(x, p + "ffn_gate_shexp.weight")
+            u = self.mm(x, p + "ffn_up_shexp.weight")
+            sh = self.mm(torch.nn.functional.silu(g) * u, p + "ffn_down_shexp.weight")
             out = out + torch.sigmoid(x @ w[p + "ffn_gate_inp_shexp.weight"].reshape(-1, 1)) * sh
         for e in range(c.n_expert):
             sel = (topi == e)
@@ -168,9 +176,9 @@ class ReferenceModel:
             if rows.numel() == 0:
                 continue
             xe = x[rows]
-            g = xe @ w[p + "ffn_gate_exps.weight"][e].T
-            u = xe @ w[p + "ffn_up_exps.weight"][e].T
-            y = (torch.nn.functional.silu(g) * u) @ w[p + "ffn_down_exps.weight"][e].T
+            g = self.mm(xe, p + "ffn_gate_exps.weight", e)
+            u = self.mm(xe, p + "ffn_up_exps.weight", e)
+            y = self.mm(torch.nn.functional.silu(g) * u, p + "ffn_down_exps.weight", e)
             we = (topw[rows] * sel[rows]).sum(-1, keepdim=True)
             out[rows] += we * y
         return out
@@ -188,7 +196,10 @@ class ReferenceModel:
     def head(self, h: torch.Tensor) -> torch.Tensor:
         c, w = self.cfg, self.w
         out_w = w.get("output.weight", w["token_embd.weight"])
-        return rms_norm(h, w["output_norm.weight"], c.rms_eps) @ out_w.T / c.logit_scale
+        xn = rms_norm(h, w["output_norm.weight"], c.rms_eps)
+        if self.observer is not None:
+            self.observer("output.weight" if "output.weight" in w else "token_embd.weight", xn, None)
+        return xn @ out_w.T / c.logit_scale
 
     # ---- full forward ---------------------------------------------------------------------
     @torch.no_grad()

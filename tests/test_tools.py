@@ -110,3 +110,46 @@ def test_serve_bench_against_orchestrator(tmp_models):
             assert all(x["ok"] == x["concurrency"] and x["agg_tok_s"] > 0 and x["ttft_ms_p50"] > 0 for x in rows), rows
     finally:
         sched.stop()
+
+
+def test_imatrix_tool_and_weighted_quantize(tmp_models, tmp_path):
+    """`dlp_imatrix.py` (llama-imatrix): the statistic, the GGUF layout the reference writes, and its use by `dlp_quantize --imatrix`."""
+    import torch
+    from distributed_llm_pipeline_b200.models.reference import ReferenceModel, rms_norm
+    model = tmp_models[("tiny-moe", "F16")]
+    imat = str(tmp_path / "imatrix.gguf")
+    out = _run("dlp_imatrix.py", "-m", model, "-c", "32", "--chunks", "3", "-o", imat)
+    assert "3 chunks of 32 tokens" in out
+    f = open_gguf(imat)
+    assert f.metadata["general.type"] == "imatrix" and f.metadata["imatrix.chunk_count"] == 3 and f.metadata["imatrix.chunk_size"] == 32
+    ref = ReferenceModel.from_gguf(model)
+    c = ref.cfg
+    # dense matrices: one row, 96 tokens each; routed experts: one row per expert, n_expert_used visits per token in total
+    assert f.array("blk.0.attn_q.weight.in_sum2").shape == (1, c.n_embd) and float(f.array("blk.0.attn_q.weight.counts")[0, 0]) == 96
+    cn = f.array("blk.1.ffn_down_exps.weight.counts")
+    assert cn.shape == (c.n_expert, 1) and float(cn.sum()) == 96 * c.n_expert_used
+    assert f.array("blk.1.ffn_down_exps.weight.in_sum2").shape == (c.n_expert, c.n_ff)
+    # the statistic itself, recomputed by hand for the first layer's Q projection: sum over tokens of rms_norm(embed)^2
+    g = torch.Generator().manual_seed(0)
+    ids = torch.randint(3, c.vocab_size, (32 * 3,), generator=g)
+    xn = rms_norm(ref.embed(ids), ref.w["blk.0.attn_norm.weight"], c.rms_eps)
+    assert np.allclose(f.array("blk.0.attn_q.weight.in_sum2")[0], (xn * xn).sum(0).numpy(), rtol=1e-4)
+    # the quantizer weighs its error by it: per-column error weighted by the mean squared activation goes down
+    plain, weighted = str(tmp_path / "plain.gguf"), str(tmp_path / "weighted.gguf")
+    _run("dlp_quantize.py", model, plain, "Q4_K_M")
+    log = _run("dlp_quantize.py", model, weighted, "Q4_K_M", "--imatrix", imat)
+    assert "tensors weighted" in log
+    src, fp, fw = open_gguf(model), open_gguf(plain), open_gguf(weighted)
+    better = 0
+    for name in ("blk.0.attn_q.weight", "blk.0.attn_output.weight", "blk.1.attn_k.weight"):
+        imp = f.array(name + ".in_sum2")[0] / 96.0
+        a = src.array(name)
+        e_plain, e_w = (imp * (fp.array(name) - a) ** 2).sum(), (imp * (fw.array(name) - a) ** 2).sum()
+        assert e_w < e_plain * 1.02, (name, e_plain, e_w)
+        better += e_w < 0.95 * e_plain
+    assert better >= 2
+    assert fw.tensors["blk.0.ffn_gate_exps.weight"].ggml_type == GGMLType.Q4_K
+    # the weighted file is still a model: it loads and tracks the F16 logits at least as well as a 4-bit file should
+    lw = ReferenceModel.from_gguf(weighted).forward(ids[:32], ReferenceModel.from_gguf(weighted).new_cache(32))
+    l16 = ref.forward(ids[:32], ref.new_cache(32))
+    assert float(((lw - l16) ** 2).sum() / (l16 ** 2).sum()) < 0.05

@@ -1,0 +1,108 @@
+#!/usr/bin/env python
+"""dlp-imatrix: importance matrix of a model over a calibration text - for every weight matrix, the sum over tokens of the
+squared activations entering each input column (per expert for routed experts).
+
+Parity: `llama-imatrix` (`llama.cpp/tools/imatrix/imatrix.cpp`): same statistic (`collect_imatrix :225-400`), same GGUF layout
+(`save_imatrix :497-600`: `general.type = "imatrix"`, `imatrix.datasets / chunk_count / chunk_size`, one `<weight>.in_sum2`
+[n_mat, K] and one `<weight>.counts` [n_mat, 1] tensor per matrix), so the file feeds either quantizer.  The forward pass is the
+fp32 graph of `models/reference.py` (every weight mat-mul goes through `ReferenceModel.mm`, which this tool observes) in chunks of
+`-c` tokens, the way the reference tool walks its dataset.
+"""
+import argparse
+import os
+import sys
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import numpy as np  # noqa: E402
+import torch  # noqa: E402
+
+from distributed_llm_pipeline_b200.gguf import GGMLType, GGUFWriter, open_gguf  # noqa: E402
+from distributed_llm_pipeline_b200.gguf.constants import ValueType  # noqa: E402
+
+
+class Collector:
+    def __init__(self, model):
+        self.model = model
+        self.sum2: dict[str, np.ndarray] = {}
+        self.counts: dict[str, np.ndarray] = {}
+
+    def __call__(self, name: str, x: torch.Tensor, expert):
+        w = self.model.w[name]
+        n_mat = w.shape[0] if w.dim() == 3 else 1
+        K = w.shape[-1]
+        if name not in self.sum2:
+            self.sum2[name] = np.zeros((n_mat, K), np.float64)
+            self.counts[name] = np.zeros((n_mat, 1), np.float64)
+        x2 = x.reshape(-1, K).double()
+        e = 0 if expert is None else int(expert)
+        self.sum2[name][e] += (x2 * x2).sum(0).numpy()
+        self.counts[name][e, 0] += x2.shape[0]
+
+
+def collect(model_path: str, token_ids: list[int], n_ctx: int, n_chunks: int, log=print):
+    from distributed_llm_pipeline_b200.models.reference import ReferenceModel
+    m = ReferenceModel.from_gguf(model_path)
+    col = Collector(m)
+    m.observer = col
+    n_chunks = min(n_chunks if n_chunks > 0 else 1 << 30, len(token_ids) // n_ctx)
+    if n_chunks < 1:
+        raise SystemExit(f"the calibration text has {len(token_ids)} tokens: fewer than one chunk of {n_ctx}")
+    for c in range(n_chunks):
+        m.forward(token_ids[c * n_ctx:(c + 1) * n_ctx], m.new_cache(n_ctx))
+        log(f"[{c + 1}/{n_chunks}] {len(col.sum2)} matrices")
+    m.observer = None
+    return col, n_chunks
+
+
+def save(path: str, col: Collector, n_chunks: int, n_ctx: int, dataset: str):
+    w = GGUFWriter(path)
+    w.add("general.type", "imatrix")
+    w.add("imatrix.datasets", [dataset], etype=ValueType.STRING)
+    w.add("imatrix.chunk_count", int(n_chunks), ValueType.UINT32)
+    w.add("imatrix.chunk_size", int(n_ctx), ValueType.UINT32)
+    for name in sorted(col.sum2):
+        s2 = col.sum2[name].astype("<f4")
+        cn = col.counts[name].astype("<f4")
+        w.add_tensor(name + ".in_sum2", s2.shape, GGMLType.F32, lambda a=s2: a.view(np.uint8).reshape(-1))
+        w.add_tensor(name + ".counts", cn.shape, GGMLType.F32, lambda a=cn: a.view(np.uint8).reshape(-1))
+    w.write()
+    return path
+
+
+def load(path: str) -> dict[str, np.ndarray]:
+    """imatrix GGUF -> {weight name: mean squared activation per input column, [n_mat, K]} (what the quantizer weighs errors by)."""
+    f = open_gguf(path)
+    if f.metadata.get("general.type") != "imatrix":
+        raise ValueError(f"{path} is not an imatrix file")
+    out = {}
+    for name in f.names():
+        if name.endswith(".in_sum2"):
+            base = name[: -len(".in_sum2")]
+            s2 = np.array(f.array(name), np.float32)
+            cn = np.array(f.array(base + ".counts"), np.float32).reshape(-1, 1)
+            out[base] = np.where(cn > 0, s2 / np.maximum(cn, 1), 0).astype(np.float32)
+    return out
+
+
+def main(argv=None):
+    ap = argparse.ArgumentParser(description=__doc__.splitlines()[0])
+    ap.add_argument("-m", "--model", required=True)
+    ap.add_argument("-f", "--file", default=None, help="calibration text (default: synthetic token ids)")
+    ap.add_argument("-o", "--output", default="imatrix.gguf")
+    ap.add_argument("-c", "--ctx-size", type=int, default=128)
+    ap.add_argument("--chunks", type=int, default=-1)
+    a = ap.parse_args(argv)
+    from distributed_llm_pipeline_b200.utils.tokenizer import Tokenizer
+    f = open_gguf(a.model)
+    if a.file:
+        ids = Tokenizer(f.metadata).encode(open(a.file, encoding="utf-8").read())
+    else:
+        g = torch.Generator().manual_seed(0)
+        ids = torch.randint(3, len(f.metadata["tokenizer.ggml.tokens"]), (a.ctx_size * max(1, a.chunks if a.chunks > 0 else 4),), generator=g).tolist()
+    col, n = collect(a.model, ids, a.ctx_size, a.chunks)
+    save(a.output, col, n, a.ctx_size, a.file or "synthetic")
+    print(f"{a.output}: {len(col.sum2)} matrices, {n} chunks of {a.ctx_size} tokens")
+
+
+if __name__ == "__main__":
+    main()

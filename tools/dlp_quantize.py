@@ -2,7 +2,8 @@
 """dlp-quantize: re-encode a GGUF checkpoint to another file type (F16 / BF16 / Q8_0 / Q6_K / Q4_K_M / Q5_K_M).
 
 Parity: `llama-quantize` (`llama.cpp/tools/quantize`, mix rules `src/llama-quant.cpp:302-405`).  Tensor-type selection is the
-same recipe `gguf/synth.py` uses; encoders are the closed-form ones of `gguf/quants.py` (no importance matrix).
+same recipe `gguf/synth.py` uses; encoders are the closed-form ones of `gguf/quants.py`; `--imatrix file.gguf` (from `dlp_imatrix.py` or the reference's
+`llama-imatrix`) switches the K-quant encoders to error-weighted fits (`llama-quant.cpp:880-960` imatrix lookup per tensor).
 """
 import argparse
 import os
@@ -22,7 +23,13 @@ def main(argv=None):
     ap.add_argument("src")
     ap.add_argument("dst")
     ap.add_argument("ftype", choices=sorted(FTYPE))
+    ap.add_argument("--imatrix", default=None, help="importance matrix GGUF: weigh quantisation error by activation statistics")
     a = ap.parse_args(argv)
+    imat = {}
+    if a.imatrix:
+        sys.path.insert(0, os.path.dirname(os.path.abspath(__file__)))
+        from dlp_imatrix import load as load_imatrix
+        imat = load_imatrix(a.imatrix)
     f = open_gguf(a.src)
     cfg = config_from_gguf(f.metadata, f.tensors)
     w = GGUFWriter(a.dst)
@@ -44,11 +51,21 @@ def main(argv=None):
         def produce(name=name, want=want, info=info):
             if want == info.ggml_type:
                 return np.ascontiguousarray(f.raw(name)).reshape(-1)
-            return quantize(f.array(name).reshape(-1, info.shape[-1]), want)
+            imp = imat.get(name)
+            x = f.array(name)
+            if imp is None or imp.shape[-1] != info.shape[-1]:
+                return quantize(x.reshape(-1, info.shape[-1]), want)
+            if imp.shape[0] == 1:
+                return quantize(x.reshape(-1, info.shape[-1]), want, imp[0])
+            # stacked experts: each expert's rows with that expert's statistics (unseen experts fall back to the plain encoder)
+            parts = [quantize(x[e].reshape(-1, info.shape[-1]), want, imp[e] if float(imp[e].sum()) > 0 else None) for e in range(x.shape[0])]
+            return np.concatenate(parts)
 
         w.add_tensor(name, info.shape, want, produce)
     w.write()
     n_out = os.path.getsize(a.dst)
+    if imat:
+        print(f"imatrix: {sum(1 for n in f.tensors if n in imat)} of {len(f.tensors)} tensors weighted")
     print(f"{a.src} -> {a.dst}  [{a.ftype}]  {n_in / 2**20:.1f} MiB -> {n_out / 2**20:.1f} MiB")
 
 
