@@ -92,13 +92,19 @@ class ReferenceModel:
         self.inv_freq = rope_inv_freq(cfg, ff)
         self.inv_freq_off = torch.zeros_like(self.inv_freq)      # zero angles = identity rotation (layers without RoPE)
 
+    lora: dict = {}     # weight name -> (A [r, K], B [N, r], scale)
     observer = None     # fn(weight_name, x [T, K], expert | None): sees the input of every weight mat-mul (imatrix collection)
 
     def mm(self, x: torch.Tensor, name: str, expert: int | None = None) -> torch.Tensor:
         w = self.w[name] if expert is None else self.w[name][expert]
         if self.observer is not None:
             self.observer(name, x, expert)
-        return x @ w.T
+        y = x @ w.T
+        ad = self.lora.get(name) if (self.lora and expert is None) else None
+        if ad is not None:          # trainable low-rank update: W + scale * B A  (tools/dlp_finetune.py --lora)
+            a, b, scale = ad
+            y = y + scale * ((x @ a.T) @ b.T)
+        return y
 
     def layer_inv_freq(self, il: int) -> torch.Tensor:
         return self.inv_freq if self.cfg.layer_uses_rope(il) else self.inv_freq_off
@@ -202,9 +208,13 @@ class ReferenceModel:
         return xn @ out_w.T / c.logit_scale
 
     # ---- full forward ---------------------------------------------------------------------
-    @torch.no_grad()
     def forward(self, tokens, cache: RefKVCache, layers: range | None = None, hidden: torch.Tensor | None = None,
                 return_hidden: bool = False) -> torch.Tensor:
+        with torch.no_grad():
+            return self.forward_grad(tokens, cache, layers, hidden, return_hidden)
+
+    def forward_grad(self, tokens, cache: RefKVCache, layers: range | None = None, hidden: torch.Tensor | None = None,
+                     return_hidden: bool = False) -> torch.Tensor:
         """Run `tokens` (appended at cache.length) through `layers` (default: all) and return logits
         [T, vocab] - or the hidden state when this is a non-final pipeline stage."""
         c = self.cfg

@@ -153,3 +153,98 @@ def test_imatrix_tool_and_weighted_quantize(tmp_models, tmp_path):
     lw = ReferenceModel.from_gguf(weighted).forward(ids[:32], ReferenceModel.from_gguf(weighted).new_cache(32))
     l16 = ref.forward(ids[:32], ref.new_cache(32))
     assert float(((lw - l16) ** 2).sum() / (l16 ** 2).sum()) < 0.05
+
+
+def test_cvector_generator(tmp_models, tmp_path):
+    """`dlp_cvector.py` (llama-cvector-generator): layer-output differences -> unit directions -> a file the engine applies."""
+    import torch
+    from distributed_llm_pipeline_b200.models.llama import LlamaEngine
+    from distributed_llm_pipeline_b200.models.reference import ReferenceModel
+    from distributed_llm_pipeline_b200.models.weights import load_weights
+    from distributed_llm_pipeline_b200.utils.tokenizer import Tokenizer
+    model = tmp_models[("tiny-smollm3", "F16")]            # 4 layers -> 3 directions
+    pos, neg = tmp_path / "pos.txt", tmp_path / "neg.txt"
+    pos.write_text("I am very happy today\nthis is wonderful news\n")
+    neg.write_text("I am very sad today\nthis is terrible news\n")
+    out = str(tmp_path / "cv.gguf")
+    for method in ("mean", "pca"):
+        log = _run("dlp_cvector.py", "-m", model, "--positive-file", str(pos), "--negative-file", str(neg), "-o", out, "--method", method, "--device", "cpu")
+        assert "3 directions of 256" in log
+        f = open_gguf(out)
+        assert f.metadata["general.architecture"] == "controlvector" and f.metadata["controlvector.layer_count"] == 3
+        assert f.metadata["controlvector.model_hint"] == "smollm3" and sorted(f.tensors) == ["direction.1", "direction.2", "direction.3"]
+        for n in f.tensors:
+            assert abs(float(np.linalg.norm(f.array(n))) - 1.0) < 1e-4
+    # "mean", recomputed with the oracle for the first layer
+    _run("dlp_cvector.py", "-m", model, "--positive-file", str(pos), "--negative-file", str(neg), "-o", out, "--method", "mean", "--device", "cpu")
+    ref, tok = ReferenceModel.from_gguf(model), Tokenizer.from_gguf(model)
+    rows = []
+    for p, n in zip(pos.read_text().splitlines(), neg.read_text().splitlines()):
+        a, b = tok.encode(p), tok.encode(n)
+        T = max(len(a), len(b))
+        padt = tok.encode(" ", add_bos=False)[-1:]
+        a, b = a + padt * (T - len(a)), b + padt * (T - len(b))
+        ha = ref.forward(a, ref.new_cache(64), layers=range(0, 1), return_hidden=True)
+        hb = ref.forward(b, ref.new_cache(64), layers=range(0, 1), return_hidden=True)
+        d = ha - hb
+        rows.append(d[d.abs().sum(-1) > 0])
+    want = torch.cat(rows).mean(0)
+    want = want / want.norm()
+    assert np.allclose(open_gguf(out).array("direction.1"), want.numpy(), atol=2e-4)
+    # applying the file moves the residual stream along the direction: the projection of layer 1's output grows with the scale
+    eng = LlamaEngine(load_weights(model, "cpu"), n_ctx=64, max_seqs=1, page_size=16, max_batch_tokens=32)
+    ids = tok.encode("this is news")
+    d1 = torch.from_numpy(np.array(open_gguf(out).array("direction.1")))
+
+    def proj(scale):
+        eng.set_control_vector(out if scale else None, scale or 1.0)
+        got = {}
+        eng.eval_callback = lambda name, il, t: got.__setitem__(il, t.float().clone())
+        sid = eng.alloc_seq()
+        eng.prefill(sid, ids)
+        eng.free_seq(sid)
+        eng.eval_callback = None
+        return float((got[1] @ d1).mean())
+    base, plus = proj(0), proj(4.0)
+    assert abs((plus - base) - 4.0) < 1e-3          # unit direction x scale, added after layer 1
+
+
+def test_finetune_full_and_lora(tmp_models, tmp_path):
+    """`dlp_finetune.py` (examples/training/finetune.cpp over ggml-opt): loss falls, the checkpoint / adapter it writes load in the engine."""
+    import random
+    import torch
+    from distributed_llm_pipeline_b200.models.llama import LlamaEngine
+    from distributed_llm_pipeline_b200.models.reference import ReferenceModel
+    from distributed_llm_pipeline_b200.models.weights import LoraAdapter, load_weights
+    from distributed_llm_pipeline_b200.utils.tokenizer import Tokenizer
+    model = tmp_models[("tiny", "F16")]
+    r = random.Random(1)
+    phrases = ["the cat sat on the mat", "a dog ran in the park", "the sun is hot today"]
+    text = tmp_path / "train.txt"
+    text.write_text(". ".join(r.choice(phrases) for _ in range(120)))
+    ids = Tokenizer.from_gguf(model).encode(text.read_text())[:33]
+
+    def nll(logits):
+        return float(torch.nn.functional.cross_entropy(logits.float(), torch.tensor(ids[1:])))
+    base = ReferenceModel.from_gguf(model)
+    nll0 = nll(base.forward(ids[:-1], base.new_cache(64)))
+    # all weights
+    out = str(tmp_path / "ft.gguf")
+    log = _run("dlp_finetune.py", "-m", model, "-f", str(text), "-o", out, "-c", "32", "--epochs", "1", "-b", "4", "--lr", "2e-3", "--outtype", "F32")
+    assert "train loss" in log and "held out" in log
+    ft = ReferenceModel.from_gguf(out)
+    assert ft.cfg == base.cfg
+    nll1 = nll(ft.forward(ids[:-1], ft.new_cache(64)))
+    assert nll1 < 0.5 * nll0, (nll0, nll1)
+    eng = LlamaEngine(load_weights(out, "cpu"), n_ctx=64, max_seqs=1, page_size=16, max_batch_tokens=64)
+    lg = eng.prefill(eng.alloc_seq(), ids[:-1], all_logits=True)
+    assert abs(nll(lg) - nll1) < 1e-3
+    # adapter only
+    ad = str(tmp_path / "lora.gguf")
+    _run("dlp_finetune.py", "-m", model, "-f", str(text), "-o", ad, "-c", "32", "--epochs", "2", "-b", "4", "--lr", "1e-2", "--lora", "4")
+    f = open_gguf(ad)
+    assert f.metadata["general.type"] == "adapter" and f.metadata["adapter.lora.alpha"] == 8.0
+    assert f.array("blk.0.attn_q.weight.lora_a").shape == (4, base.cfg.n_embd) and "blk.1.ffn_down.weight.lora_b" in f.tensors
+    eng2 = LlamaEngine(load_weights(model, "cpu", lora=[LoraAdapter(ad)]), n_ctx=64, max_seqs=1, page_size=16, max_batch_tokens=64)
+    nll2 = nll(eng2.prefill(eng2.alloc_seq(), ids[:-1], all_logits=True))
+    assert nll2 < 0.8 * nll0, (nll0, nll2)
