@@ -80,3 +80,48 @@ def test_converted_model_matches_hf_forward(tmp_path, family):
     eng = LlamaEngine(load_weights(out, "cpu"), n_ctx=64, max_seqs=1, page_size=16, max_batch_tokens=32)
     lg = eng.prefill(eng.alloc_seq(), ids)
     assert nmse(want[-1], lg.float().flatten()) < 1e-5
+
+
+@pytest.mark.parametrize("family", ["llama", "qwen2"])
+def test_converted_lora_adapter_matches_merged_hf_model(tmp_path, family):
+    """convert_lora_to_gguf.py: base model and a PEFT-layout adapter converted separately; engine(base + adapter) == the HF model with
+    W + (alpha / r) B A merged in (for llama this pins the Q/K row permutation of the B factors)."""
+    import json
+    from safetensors.torch import save_file
+    cfg_cls, model_cls, extra = CASES[family]
+    torch.manual_seed(1)
+    cfg = getattr(transformers, cfg_cls)(**{**COMMON, **extra})
+    model = getattr(transformers, model_cls)(cfg).eval().float()
+    base_dir = tmp_path / "base"
+    model.save_pretrained(str(base_dir), safe_serialization=True)
+    r, alpha = 4, 8.0
+    targets = ["self_attn.q_proj", "self_attn.k_proj", "self_attn.v_proj", "self_attn.o_proj", "mlp.down_proj"]
+    lora = {}
+    with torch.no_grad():
+        for il, layer in enumerate(model.model.layers):
+            for tname in targets:
+                mod = layer.get_submodule(tname)
+                A, B = torch.randn(r, mod.in_features) * 0.05, torch.randn(mod.out_features, r) * 0.05
+                lora[f"base_model.model.model.layers.{il}.{tname}.lora_A.weight"] = A
+                lora[f"base_model.model.model.layers.{il}.{tname}.lora_B.weight"] = B
+                mod.weight += (alpha / r) * (B @ A)             # the HF model now IS base + adapter
+    ad_dir = tmp_path / "adapter"
+    ad_dir.mkdir()
+    save_file(lora, str(ad_dir / "adapter_model.safetensors"))
+    json.dump({"peft_type": "LORA", "r": r, "lora_alpha": alpha, "target_modules": [t.split(".")[-1] for t in targets], "bias": "none"},
+              open(ad_dir / "adapter_config.json", "w"))
+    conv = importlib.import_module("convert_hf_to_gguf")
+    base_gguf = conv.convert(str(base_dir), str(tmp_path / "base.gguf"), "F32")
+    lconv = importlib.import_module("convert_lora_to_gguf")
+    ad_gguf = lconv.convert(str(ad_dir), str(base_dir), str(tmp_path / "adapter.gguf"))
+    from distributed_llm_pipeline_b200.models.llama import LlamaEngine
+    from distributed_llm_pipeline_b200.models.reference import nmse
+    from distributed_llm_pipeline_b200.models.weights import LoraAdapter, load_weights
+    ids = [1, 5, 9, 200, 33, 7, 8, 100, 42, 17, 3, 250]
+    with torch.no_grad():
+        want = model(torch.tensor([ids])).logits[0, -1]
+    eng = LlamaEngine(load_weights(base_gguf, "cpu", lora=[LoraAdapter(ad_gguf)]), n_ctx=64, max_seqs=1, page_size=16, max_batch_tokens=32)
+    got = eng.prefill(eng.alloc_seq(), ids).float().flatten()
+    assert nmse(want, got) < 1e-5
+    plain = LlamaEngine(load_weights(base_gguf, "cpu"), n_ctx=64, max_seqs=1, page_size=16, max_batch_tokens=32)
+    assert nmse(want, plain.prefill(plain.alloc_seq(), ids).float().flatten()) > 1e-3      # the adapter matters

@@ -248,3 +248,36 @@ def test_finetune_full_and_lora(tmp_models, tmp_path):
     eng2 = LlamaEngine(load_weights(model, "cpu", lora=[LoraAdapter(ad)]), n_ctx=64, max_seqs=1, page_size=16, max_batch_tokens=64)
     nll2 = nll(eng2.prefill(eng2.alloc_seq(), ids[:-1], all_logits=True))
     assert nll2 < 0.8 * nll0, (nll0, nll2)
+
+
+def test_gguf_dump_hash_and_metadata_edit(tmp_models, tmp_path):
+    """`dlp_gguf.py`: gguf_dump / gguf_hash / gguf_set_metadata / gguf_new_metadata."""
+    import json
+    import shutil
+    src = tmp_models[("tiny", "Q8_0")]
+    out = _run("dlp_gguf.py", "dump", src)
+    assert "general.architecture = 'llama'" in out and "blk.0.attn_q.weight" in out and "Q8_0" in out
+    d = json.loads(_run("dlp_gguf.py", "dump", src, "--json"))
+    assert d["metadata"]["llama.block_count"] == 2 and d["tensors"]["output_norm.weight"]["type"] == "F32"
+    a = str(tmp_path / "a.gguf")
+    shutil.copy(src, a)
+    h1 = _run("dlp_gguf.py", "hash", "-q", a).split()[1]
+    # in place: same-size values only
+    _run("dlp_gguf.py", "set-metadata", a, "llama.context_length", "4096")
+    assert open_gguf(a).metadata["llama.context_length"] == 4096
+    name = open_gguf(a).metadata["general.name"]
+    _run("dlp_gguf.py", "set-metadata", a, "general.name", name[::-1])
+    assert open_gguf(a).metadata["general.name"] == name[::-1]
+    r = subprocess.run([sys.executable, os.path.join(REPO, "tools", "dlp_gguf.py"), "set-metadata", a, "general.name", "longer-than-before-xyz"], capture_output=True, text=True)
+    assert r.returncode != 0 and "new-metadata" in r.stderr
+    # rewrite: add / replace / remove keys, tensor bytes untouched
+    b = str(tmp_path / "b.gguf")
+    _run("dlp_gguf.py", "new-metadata", a, b, "--set", "general.name=renamed model", "--set", "general.description=test file", "--set", "llama.rope.freq_base=500000.0",
+         "--set", "custom.answer:uint32=42", "--remove", "tokenizer.ggml.pre")
+    fb = open_gguf(b)
+    assert fb.metadata["general.name"] == "renamed model" and fb.metadata["general.description"] == "test file" and fb.metadata["custom.answer"] == 42
+    assert abs(fb.metadata["llama.rope.freq_base"] - 500000.0) < 1 and "tokenizer.ggml.pre" not in fb.metadata
+    assert _run("dlp_gguf.py", "hash", "-q", b).split()[1] == h1          # metadata edits do not touch the weights
+    assert "same tensor data" in _run("dlp_gguf.py", "hash", "-q", b, "--check", src)
+    r = subprocess.run([sys.executable, os.path.join(REPO, "tools", "dlp_gguf.py"), "hash", "-q", b, "--check", tmp_models[("tiny", "F16")]], capture_output=True, text=True)
+    assert r.returncode == 1 and "DIFFERENT" in r.stdout
