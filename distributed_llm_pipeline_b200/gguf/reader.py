@@ -87,13 +87,25 @@ class _Cursor:
 class GGUFFile:
     """One GGUF file (or a set of split shards opened through :func:`open_gguf`)."""
 
-    def __init__(self, path: str):
+    def __init__(self, path: str, use_mmap: bool | None = None, mlock: bool | None = None, direct_io: bool | None = None):
+        """use_mmap=False reads the file into anonymous memory instead of mapping it (`--no-mmap`), direct_io=True does that with
+        O_DIRECT so the page cache is bypassed (`--direct-io`), mlock=True pins the pages (`--mlock`) - the loader options of
+        `llama.cpp/src/llama-mmap.cpp` (llama_mmap / llama_mlock / llama_file direct I/O).  None: DLP_NO_MMAP / DLP_DIRECT_IO /
+        DLP_MLOCK from the environment (how the command-line flags reach every tool)."""
         self.path = path
+        use_mmap = os.environ.get("DLP_NO_MMAP", "0") != "1" if use_mmap is None else use_mmap
+        direct_io = os.environ.get("DLP_DIRECT_IO", "0") == "1" if direct_io is None else direct_io
+        mlock = os.environ.get("DLP_MLOCK", "0") == "1" if mlock is None else mlock
         self._fh = open(path, "rb")
         size = os.fstat(self._fh.fileno()).st_size
         if size < 24:
             raise ValueError(f"{path}: not a GGUF file (too small)")
-        self._mm = mmap.mmap(self._fh.fileno(), 0, access=mmap.ACCESS_READ)
+        self.load_mode = "mmap"
+        if use_mmap and not direct_io:
+            self._mm = mmap.mmap(self._fh.fileno(), 0, access=mmap.ACCESS_READ)
+        else:
+            self._mm = self._read_all(path, size, direct_io)
+        self.mlocked = self._mlock(size) if mlock else False
         cur = _Cursor(self._mm)
         if cur.take("<I") != GGUF_MAGIC:
             raise ValueError(f"{path}: bad magic")
@@ -129,6 +141,57 @@ class GGUFFile:
         for t in self.tensors.values():
             if self.data_offset + t.offset + t.nbytes > size:
                 raise ValueError(f"{path}: tensor {t.name} extends past end of file")
+
+    def _read_all(self, path: str, size: int, direct_io: bool):
+        """The whole file in page-aligned anonymous memory; with direct_io the reads bypass the page cache (block-aligned chunks
+        through O_DIRECT, the unaligned tail through the ordinary descriptor)."""
+        buf = mmap.mmap(-1, max(size, 1))
+        view = memoryview(buf)
+        done = 0
+        self.load_mode = "read"
+        if direct_io and hasattr(os, "O_DIRECT"):
+            try:
+                fd = os.open(path, os.O_RDONLY | os.O_DIRECT)
+            except OSError:
+                fd = -1          # tmpfs and friends refuse O_DIRECT: fall back to buffered reads
+            if fd >= 0:
+                try:
+                    blk, chunk = 4096, 64 << 20
+                    aligned = size // blk * blk
+                    while done < aligned:
+                        n = os.preadv(fd, [view[done:min(aligned, done + chunk)]], done)
+                        if n <= 0:
+                            break
+                        done += n
+                    if done == aligned:
+                        self.load_mode = "direct"
+                    else:
+                        done = 0
+                except OSError:
+                    done = 0
+                finally:
+                    os.close(fd)
+        self._fh.seek(done)
+        while done < size:
+            n = self._fh.readinto(view[done:])
+            if not n:
+                raise ValueError(f"{path}: short read")
+            done += n
+        return buf
+
+    def _mlock(self, size: int) -> bool:
+        import ctypes
+        try:
+            addr = np.frombuffer(self._mm, dtype=np.uint8, count=1).ctypes.data
+            libc = ctypes.CDLL(None, use_errno=True)
+            if libc.mlock(ctypes.c_void_p(addr), ctypes.c_size_t(size)) != 0:
+                err = ctypes.get_errno()
+                import warnings
+                warnings.warn(f"mlock of {size / 2**20:.0f} MiB failed ({os.strerror(err)}): raise RLIMIT_MEMLOCK (ulimit -l) - continuing unlocked")
+                return False
+            return True
+        except (OSError, AttributeError, ValueError):
+            return False
 
     # ---- tensor access --------------------------------------------------------------------
     def raw(self, name: str) -> np.ndarray:

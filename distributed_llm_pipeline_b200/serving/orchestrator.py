@@ -385,7 +385,11 @@ class Orchestrator:
             schema = rf.get("schema") or {}
         if schema is None and rf.get("type") == "json_schema":
             schema = (rf.get("json_schema") or {}).get("schema") or {}
+        trig = d.get("grammar_triggers") or []       # [{"type": "word" | "pattern" | 0..3, "value": "..."}] (server-common.cpp)
+        words = tuple(str(t.get("value", "")) for t in trig if isinstance(t, dict) and t.get("type") in ("word", 1, None))
+        pats = tuple(str(t.get("value", "")) for t in trig if isinstance(t, dict) and t.get("type") in ("pattern", "pattern_full", 2, 3))
         return SamplingParams(grammar=str(d.get("grammar", "") or ""), json_schema=schema,
+                              grammar_lazy=bool(d.get("grammar_lazy", False)), grammar_trigger_words=words, grammar_trigger_patterns=pats,
                               infill=bool(d.get("infill_sampler", False)) or "infill" in (d.get("samplers") or []),
                               top_n_sigma=float(d.get("top_n_sigma", -1.0)), dynatemp_range=float(d.get("dynatemp_range", 0.0)),
                               dynatemp_exponent=float(d.get("dynatemp_exponent", 1.0)), xtc_probability=float(d.get("xtc_probability", 0.0)),
@@ -728,6 +732,9 @@ def add_parallel_args(ap):
     ap.add_argument("--workers", type=int, default=0, help="launch this many local dlp-worker stages and use them (implies --rpc)")
     ap.add_argument("--worker-base-port", type=int, default=50052)
     ap.add_argument("--no-warmup", action="store_true", help="skip the start-up warm-up (kernel set-up + decode-graph capture per batch size)")
+    ap.add_argument("--mlock", action="store_true", help="pin the model file's pages in RAM")
+    ap.add_argument("--no-mmap", action="store_true", help="read the model file into memory instead of mapping it")
+    ap.add_argument("--direct-io", action="store_true", help="read the model file with O_DIRECT (implies --no-mmap)")
     ap.add_argument("-md", "--model-draft", default=os.environ.get("DLP_ARG_MODEL_DRAFT"),
                     help="draft model (same vocabulary) for speculative decoding of greedy requests inside the server")
     ap.add_argument("--draft-max", type=int, default=16, help="tokens drafted per verification block (0 = off unless the request asks)")
@@ -823,6 +830,8 @@ def build_service(model: str, device: str = "cuda", n_ctx: int = 2048, n_slots: 
 
 
 def service_kwargs(a) -> dict:
+    from ..utils.args import apply_loader_flags
+    apply_loader_flags(a)
     return dict(pp=a.pp, tp=a.tp, tp_impl=a.tp_impl, tensor_split=a.tensor_split, rpc=a.rpc, workers=a.workers,
                 worker_base_port=a.worker_base_port, model_draft=getattr(a, "model_draft", None), draft_max=getattr(a, "draft_max", 16))
 

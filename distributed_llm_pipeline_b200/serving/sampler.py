@@ -41,6 +41,12 @@ class SamplingParams:
     dry_breakers: tuple = ()           # token ids that end a repeated span (the reference's sequence breakers, tokenised)
     grammar: str = ""                  # GBNF text; "" = unconstrained
     json_schema: dict | None = None    # converted to GBNF when `grammar` is empty
+    # lazy grammar (`llama_sampler_init_grammar_lazy_patterns`, llama-sampling.cpp:2625-2775): the grammar stays off until the
+    # generated text contains one of the trigger words / matches one of the trigger regexes; from the start of that match on, the
+    # output must follow the grammar (tool-call syntaxes: free text first, then a strictly formed call)
+    grammar_lazy: bool = False
+    grammar_trigger_words: tuple = ()
+    grammar_trigger_patterns: tuple = ()
     infill: bool = False               # fill-in-the-middle filter: prefer ending over low-confidence text, merge prefix-sharing tokens
 
     @property
@@ -215,11 +221,30 @@ class Sampler:
                 raise ValueError("grammar-constrained sampling needs the tokenizer")
             from .grammar import GrammarConstraint
             self.constraint = GrammarConstraint(gtext, tokenizer.token_texts(), tuple(tokenizer.stop_ids))
+            if params.grammar_lazy and (params.grammar_trigger_words or params.grammar_trigger_patterns):
+                import re
+                self._pending = self.constraint          # armed by a trigger
+                self.constraint = None
+                self._trig = [re.compile(re.escape(w)) for w in params.grammar_trigger_words] + [re.compile(p) for p in params.grammar_trigger_patterns]
+                self._texts = tokenizer.token_texts()
+                self._seen = ""
+
+    _pending = None
 
     def accept(self, token: int):
         self.history.append(token)
         if self.constraint is not None:
             self.constraint.accept(token)
+        elif self._pending is not None:
+            self._seen += self._texts[token] or ""
+            hit = min((m.start() for m in (t.search(self._seen) for t in self._trig) if m), default=None)
+            if hit is not None:
+                tail = self._seen[hit:]
+                if self._pending.g.accepts(tail):        # the grammar starts at the trigger and consumes what is already out
+                    self._pending.g.accept(tail)
+                    self.constraint, self._pending = self._pending, None
+                else:                                    # the triggering token ran past what the grammar allows: stay unconstrained
+                    self._seen = self._seen[hit + 1:]
 
     def _pick(self, row: torch.Tensor) -> int:
         p = self.p

@@ -40,6 +40,9 @@ COMMON = [
     Opt(("-fa", "--flash-attn"), "accepted for compatibility: attention is always flash", "on", str, "DLP_ARG_FLASH_ATTN"),
     Opt(("--lora",), "comma separated LoRA adapter GGUFs, each optionally path:scale (merged at load)", None, str, "DLP_ARG_LORA"),
     Opt(("--device",), "cuda | cpu", "cuda", str, "DLP_ARG_DEVICE"),
+    Opt(("--mlock",), "pin the model file's pages in RAM (no swapping)", False, None, "DLP_MLOCK", action="store_true"),
+    Opt(("--no-mmap",), "read the model file into memory instead of mapping it", False, None, "DLP_NO_MMAP", action="store_true"),
+    Opt(("--direct-io",), "read the model file with O_DIRECT (bypasses the page cache; implies --no-mmap)", False, None, "DLP_DIRECT_IO", action="store_true"),
     Opt(("--list-devices",), "print the available devices and exit", False, None, action="store_true"),
     Opt(("--fit",), "shrink -c / -np until weights + KV cache fit the device memory", False, None, "DLP_ARG_FIT", action="store_true"),
     Opt(("-v", "--verbose"), "debug logging", False, None, "DLP_ARG_VERBOSE", action="store_true"),
@@ -101,6 +104,14 @@ def build_parser(description: str, groups: list[list[Opt]]) -> argparse.Argument
                     kw["choices"] = o.choices
             ap.add_argument(*o.names, **kw)
     return ap
+
+
+def apply_loader_flags(a):
+    """`--mlock / --no-mmap / --direct-io` -> the environment switches `gguf.reader.GGUFFile` reads (so every loader in the
+    process, including worker ranks started later, sees them)."""
+    for flag, env in (("mlock", "DLP_MLOCK"), ("no_mmap", "DLP_NO_MMAP"), ("direct_io", "DLP_DIRECT_IO")):
+        if getattr(a, flag, False):
+            os.environ[env] = "1"
 
 
 def sampling_from_args(a):

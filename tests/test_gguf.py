@@ -137,3 +137,25 @@ def test_truncated_file_is_rejected(tmp_path):
     bad.write_bytes(data[: len(data) // 2])
     with pytest.raises(ValueError):
         open_gguf(str(bad))
+
+
+def test_loader_modes_mmap_read_direct_mlock(tmp_path, monkeypatch):
+    """`--no-mmap`, `--direct-io`, `--mlock` (llama-mmap.cpp): every mode yields the same bytes; a refused mlock only warns."""
+    import warnings
+    from distributed_llm_pipeline_b200.gguf.reader import GGUFFile
+    path = write_synthetic_gguf(str(tmp_path / "m.gguf"), preset("tiny"), "Q8_0")
+    base = GGUFFile(path)
+    assert base.load_mode == "mmap" and not base.mlocked
+    want = {n: np.array(base.raw(n)) for n in base.tensors}
+    rd = GGUFFile(path, use_mmap=False)
+    assert rd.load_mode == "read" and all(np.array_equal(rd.raw(n), want[n]) for n in want)
+    di = GGUFFile(path, direct_io=True)
+    assert di.load_mode in ("direct", "read")                 # tmpfs refuses O_DIRECT: buffered fallback
+    assert all(np.array_equal(di.raw(n), want[n]) for n in want) and list(di.metadata) == list(base.metadata)
+    with warnings.catch_warnings(record=True) as w:
+        warnings.simplefilter("always")
+        ml = GGUFFile(path, mlock=True)
+        assert ml.mlocked or any("mlock" in str(x.message) for x in w)
+    assert all(np.array_equal(ml.raw(n), want[n]) for n in want)
+    monkeypatch.setenv("DLP_NO_MMAP", "1")                    # what --no-mmap sets for every loader in the process
+    assert open_gguf(path).files[0].load_mode == "read"

@@ -197,3 +197,39 @@ def test_infill_sampler_rules():
     s = Sampler(sp, Tok())
     assert s.sample(lp([0.05, 0.3, 0.2, 0.1, 0.2, 0.1, 0.05, 0.0001])) in (0, 6)
     assert s.sample(lp([1e-9, 0.35, 0.25, 0.15, 0.15, 0.1 - 2e-9, 1e-9, 1e-9])) == 1
+
+
+def test_lazy_grammar_is_armed_by_a_trigger():
+    """grammar_lazy + trigger words / patterns: free text until the trigger shows up in the output, the grammar (which starts at the
+    trigger) from then on (`llama_sampler_init_grammar_lazy_patterns`)."""
+    from distributed_llm_pipeline_b200.serving.sampler import Sampler, SamplingParams
+    pieces = ["<eos>", "hello ", "world ", "<call>", "{", "}", '"a"', ":", "1", "x", "<ca", "ll>"]
+
+    class Tok:
+        eot_id, eos_id, stop_ids = None, 0, {0}
+
+        def token_texts(self):
+            return [None] + pieces[1:]
+    gr = 'root ::= "<call>" "{" "\\"a\\"" ":" "1" "}"'
+
+    def run(params, script):
+        s = Sampler(params, Tok())
+        out = []
+        for favourite in script:          # logits that prefer `favourite`, then everything else equally
+            row = torch.zeros(len(pieces))
+            row[favourite] = 5.0
+            out.append(s.sample(row))
+        return out
+    lazy = SamplingParams(temperature=0.0, grammar=gr, grammar_lazy=True, grammar_trigger_words=("<call>",))
+    # free text first (a plain grammar would have refused "hello "), then the call is forced token by token whatever the logits prefer
+    got = run(lazy, [1, 2, 3, 9, 9, 9, 9, 9, 9])
+    assert got[:3] == [1, 2, 3] and "".join(pieces[t] for t in got[3:8]) == '{"a":1}' and got[8] == 0       # ... and EOS once complete
+    # a trigger split over two tokens still arms the grammar
+    got = run(lazy, [1, 10, 11, 9, 9, 9, 9, 9])
+    assert "".join(pieces[t] for t in got[1:8]) == '<call>{"a":1}'
+    # regex trigger
+    pat = SamplingParams(temperature=0.0, grammar=gr, grammar_lazy=True, grammar_trigger_patterns=(r"<c[a-z]+>",))
+    assert "".join(pieces[t] for t in run(pat, [2, 3, 9, 9, 9, 9, 9])[1:]) == '<call>{"a":1}'
+    # not lazy: constrained from the first token
+    eager = SamplingParams(temperature=0.0, grammar=gr)
+    assert run(eager, [1])[0] == 3

@@ -14,7 +14,7 @@ sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 
 import torch  # noqa: E402
 
-from distributed_llm_pipeline_b200.utils.args import COMMON, Opt, build_parser  # noqa: E402
+from distributed_llm_pipeline_b200.utils.args import COMMON, Opt, apply_loader_flags, build_parser  # noqa: E402
 
 BENCH = [
     Opt(("-p", "--n-prompt"), "comma separated prompt sizes", "512", str),
@@ -28,6 +28,7 @@ BENCH = [
 
 def main(argv=None):
     a = build_parser("dlp-bench", [COMMON, BENCH]).parse_args(argv)
+    apply_loader_flags(a)
     from distributed_llm_pipeline_b200.models.llama import LlamaEngine
     from distributed_llm_pipeline_b200.models.weights import load_weights
     from distributed_llm_pipeline_b200.parallel.grid import init_grid, stage_layer_ranges

@@ -11,12 +11,13 @@ import time
 
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 
-from distributed_llm_pipeline_b200.utils.args import COMMON, GENERATION, SAMPLING, SPECULATIVE, build_parser, lora_from_args, sampling_from_args  # noqa: E402
+from distributed_llm_pipeline_b200.utils.args import COMMON, GENERATION, SAMPLING, SPECULATIVE, apply_loader_flags, build_parser, lora_from_args, sampling_from_args  # noqa: E402
 from distributed_llm_pipeline_b200.utils.log import get_logger  # noqa: E402
 
 
 def main(argv=None):
     a = build_parser("dlp-cli - generate text from a GGUF model", [COMMON, SAMPLING, GENERATION, SPECULATIVE]).parse_args(argv)
+    apply_loader_flags(a)
     if a.list_devices:
         from distributed_llm_pipeline_b200.utils.fit import list_devices
         print("Available devices:\n  " + "\n  ".join(list_devices()))
