@@ -289,6 +289,15 @@ int dlp_rmsnorm(float* h, const float* delta, const float* w, void* out_f16, int
     return rmsnorm(h, delta, w, (__half*)out_f16, T, E, eps, (cudaStream_t)stream);
 }
 
+int dlp_layernorm(float* h, const float* delta, const float* w, const float* b, void* out_f16, int T, int E, float eps, void* stream) {
+    DLP_REQUIRE(h, "dlp_layernorm: null argument");
+    return layernorm(h, delta, w, b, (__half*)out_f16, T, E, eps, (cudaStream_t)stream);
+}
+int dlp_bias_act(const float* x, const float* bias, void* out_f16, int T, int F, int act, void* stream) {
+    DLP_REQUIRE(x && out_f16, "dlp_bias_act: null argument");
+    return bias_act(x, bias, (__half*)out_f16, T, F, act, (cudaStream_t)stream);
+}
+
 int dlp_rope_kv(const void* qkv, int qkv_is_f16, const int32_t* pos, const int32_t* slot, const float* inv_freq,
                 void* q_out, void* k_cache, void* v_cache, int T, int Hq, int Hkv, int D, int n_rot, int page_size,
                 int neox, float q_scale, void* stream) {

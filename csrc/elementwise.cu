@@ -128,6 +128,97 @@ int rmsnorm(float* h, const float* delta, const float* w, __half* out, int T, in
 }
 
 // ---------------------------------------------------------------------------------------------
+// LayerNorm (the LLM_NORM families: starcoder2, falcon, olmo, command-r, orion):
+//   h (fp32) [+= delta]  ->  out fp16 = (h - mean) * rsqrt(var + eps) * w + b      (w, b optional: olmo has neither, command-r no b)
+// Two passes over the row for the variance (mean first): the row is at most a few tens of KB and stays in L1/L2.
+// ref: norm_f32 (ggml-cuda/norm.cu:5-45) followed by the mul / add nodes of build_norm.
+__global__ void __launch_bounds__(256) layernorm_kernel(float* __restrict__ h, const float* __restrict__ delta, const float* __restrict__ w,
+                                                        const float* __restrict__ b, __half* __restrict__ out, int E, float eps) {
+    __shared__ float red[32];
+    const size_t base = (size_t)blockIdx.x * E;
+    pdl_wait();
+    pdl_launch_dependents();
+    float sum = 0.f;
+    for (int k = threadIdx.x * 4; k < E; k += blockDim.x * 4) {
+        float4 v = *reinterpret_cast<const float4*>(h + base + k);
+        if (delta) {
+            const float4 d = *reinterpret_cast<const float4*>(delta + base + k);
+            v.x += d.x; v.y += d.y; v.z += d.z; v.w += d.w;
+            *reinterpret_cast<float4*>(h + base + k) = v;
+        }
+        sum += v.x + v.y + v.z + v.w;
+    }
+    const float mean = block_sum(sum, red) / (float)E;
+    float ss = 0.f;
+    for (int k = threadIdx.x * 4; k < E; k += blockDim.x * 4) {      // each thread re-reads exactly the elements it wrote above
+        const float4 v = *reinterpret_cast<const float4*>(h + base + k);
+        const float a = v.x - mean, c = v.y - mean, d = v.z - mean, e = v.w - mean;
+        ss += a * a + c * c + d * d + e * e;
+    }
+    const float rs = rsqrtf(block_sum(ss, red) / (float)E + eps);
+    if (out == nullptr) return;
+    for (int k = threadIdx.x * 4; k < E; k += blockDim.x * 4) {
+        const float4 v = *reinterpret_cast<const float4*>(h + base + k);
+        float4 g = make_float4(1.f, 1.f, 1.f, 1.f), o4 = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (w) g = *reinterpret_cast<const float4*>(w + k);
+        if (b) o4 = *reinterpret_cast<const float4*>(b + k);
+        __half2 lo = __floats2half2_rn((v.x - mean) * rs * g.x + o4.x, (v.y - mean) * rs * g.y + o4.y);
+        __half2 hi = __floats2half2_rn((v.z - mean) * rs * g.z + o4.z, (v.w - mean) * rs * g.w + o4.w);
+        uint2 o;
+        o.x = *reinterpret_cast<uint32_t*>(&lo);
+        o.y = *reinterpret_cast<uint32_t*>(&hi);
+        *reinterpret_cast<uint2*>(out + base + k) = o;
+    }
+}
+
+int layernorm(float* h, const float* delta, const float* w, const float* b, __half* out, int T, int E, float eps, cudaStream_t s) {
+    DLP_REQUIRE(E % 4 == 0 && T > 0, "layernorm: bad shape T=%d E=%d", T, E);
+    DLP_CHECK_CUDA(launch_pdl(layernorm_kernel, dim3(T), dim3(256), 0, s, h, delta, w, b, out, E, eps));
+    return 0;
+}
+
+// ---------------------------------------------------------------------------------------------
+// Bias + activation between the two mat-muls of a non-gated MLP:  out fp16 [T, F] = act(x fp32 [T, F] + bias[F]).
+// act: 0 identity, 1 GELU (tanh form, what ggml's GELU computes), 2 ReLU^2, 3 SiLU, 4 GELU (erf form).
+// ref: gelu / silu / relu + sqr (ggml-cuda/unary.cu), bias add (binbcast.cu).
+__device__ __forceinline__ float act_apply(float v, int act) {
+    switch (act) {
+        case 1: { const float u = 0.7978845608028654f * v * (1.f + 0.044715f * v * v); return 0.5f * v * (1.f + tanhf(u)); }
+        case 2: { const float r = fmaxf(v, 0.f); return r * r; }
+        case 3: return v / (1.f + __expf(-v));
+        case 4: return 0.5f * v * (1.f + erff(v * 0.7071067811865476f));
+        default: return v;
+    }
+}
+
+__global__ void __launch_bounds__(256) bias_act_kernel(const float* __restrict__ x, const float* __restrict__ bias, __half* __restrict__ out,
+                                                       size_t n4, int F, int act) {
+    pdl_wait();
+    pdl_launch_dependents();
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += (size_t)gridDim.x * blockDim.x) {
+        float4 v = *reinterpret_cast<const float4*>(x + i * 4);
+        if (bias) {
+            const float4 b = *reinterpret_cast<const float4*>(bias + (i * 4) % (size_t)F);
+            v.x += b.x; v.y += b.y; v.z += b.z; v.w += b.w;
+        }
+        __half2 lo = __floats2half2_rn(act_apply(v.x, act), act_apply(v.y, act));
+        __half2 hi = __floats2half2_rn(act_apply(v.z, act), act_apply(v.w, act));
+        uint2 o;
+        o.x = *reinterpret_cast<uint32_t*>(&lo);
+        o.y = *reinterpret_cast<uint32_t*>(&hi);
+        *reinterpret_cast<uint2*>(out + i * 4) = o;
+    }
+}
+
+int bias_act(const float* x, const float* bias, __half* out, int T, int F, int act, cudaStream_t s) {
+    DLP_REQUIRE(F % 4 == 0 && T > 0 && act >= 0 && act <= 4, "bias_act: bad arguments T=%d F=%d act=%d", T, F, act);
+    const size_t n4 = (size_t)T * F / 4;
+    const int blocks = (int)std::min<size_t>((n4 + 255) / 256, (size_t)148 * 8);
+    DLP_CHECK_CUDA(launch_pdl(bias_act_kernel, dim3(blocks), dim3(256), 0, s, x, bias, out, n4, F, act));
+    return 0;
+}
+
+// ---------------------------------------------------------------------------------------------
 // RoPE (adjacent-pair "norm" or half-split "neox") on Q and K, fused with the paged-KV write of K and V.
 //   qkv   : [T, (Hq + 2*Hkv) * D]  fp32 or fp16 (row = q heads | k heads | v heads)
 //   q_out : [T, Hq * D] fp16 (rotated, pre-scaled by q_scale)

@@ -148,6 +148,8 @@ int moe_combine(const float* y, const int* pos, const float* w, int T, int top_k
 int dequant_rows_f32(const QWeight& w, int wtype, const int* row_ids, int n_rows, float* out, int ld_out, cudaStream_t s);
 int dequant_rows_f16(const QWeight& w, int wtype, const int* row_ids, int n_rows, __half* out, int ld_out, cudaStream_t s);
 int rmsnorm(float* h, const float* delta, const float* w, __half* out, int T, int E, float eps, cudaStream_t s);
+int layernorm(float* h, const float* delta, const float* w, const float* b, __half* out, int T, int E, float eps, cudaStream_t s);
+int bias_act(const float* x, const float* bias, __half* out, int T, int F, int act, cudaStream_t s);
 int rope_kv(const void* qkv, int qkv_is_f16, const int* pos, const int* slot, const float* inv_freq, __half* q_out,
             __half* kc, __half* vc, int T, int Hq, int Hkv, int D, int n_rot, int page_size, int neox, float q_scale,
             cudaStream_t s, const float* bias = nullptr, const float* qn = nullptr, const float* kn = nullptr, float eps = 0.f,

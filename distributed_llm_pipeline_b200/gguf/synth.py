@@ -114,15 +114,29 @@ def synthetic_vocab(n_vocab: int) -> tuple[list[str], np.ndarray, np.ndarray]:
     return tokens[:n_vocab], np.asarray(scores[:n_vocab], np.float32), np.asarray(types[:n_vocab], np.int32)
 
 
+def norm_layout(cfg: ModelConfig) -> dict:
+    """Which norm tensors a family's files carry: {"attn": "wb" | "w" | "", "ffn": ..., "out": ...} ("" = the tensor is absent)."""
+    if cfg.norm_type != "layer":
+        return {"attn": "w", "ffn": "w", "out": "w"}
+    return {"starcoder2": {"attn": "wb", "ffn": "wb", "out": "wb"}, "orion": {"attn": "wb", "ffn": "wb", "out": "wb"},
+            "falcon": {"attn": "wb", "ffn": "", "out": "wb"}, "command-r": {"attn": "w", "ffn": "", "out": "w"},
+            "olmo": {"attn": "", "ffn": "", "out": ""}}.get(cfg.arch, {"attn": "wb", "ffn": "" if cfg.parallel_residual else "wb", "out": "wb"})
+
+
 def _tensor_plan(cfg: ModelConfig, rope_freqs: bool):
     """(name, shape, layer, init_std) for every tensor of the architecture; shapes row-major [out, in]."""
     E, F = cfg.n_embd, cfg.n_ff
+    nl = norm_layout(cfg)
+    all_bias = cfg.arch == "starcoder2"       # biases on the attention output and the MLP as well
+
+    def norm(name, il, kind):
+        return ([(name + ".weight", (E,), il, 0.0)] if "w" in kind else []) + ([(name + ".bias", (E,), il, 0.05)] if "b" in kind else [])
     plan = [("token_embd.weight", (cfg.vocab_size, E), -1, 0.02)]
     if rope_freqs:
         plan.append(("rope_freqs.weight", (cfg.rope_dim // 2,), -1, 0.0))
     for il in range(cfg.n_layer):
         p = f"blk.{il}."
-        plan.append((p + "attn_norm.weight", (E,), il, 0.0))
+        plan += norm(p + "attn_norm", il, nl["attn"])
         if cfg.fused_qkv:
             plan.append((p + "attn_qkv.weight", (cfg.q_dim + 2 * cfg.kv_dim, E), il, 0.02))
         else:
@@ -134,11 +148,18 @@ def _tensor_plan(cfg: ModelConfig, rope_freqs: bool):
                      (p + "attn_v.bias", (cfg.kv_dim,), il, 0.05)]
         if cfg.qk_norm:
             plan += [(p + "attn_q_norm.weight", (cfg.head_dim,), il, 0.0), (p + "attn_k_norm.weight", (cfg.head_dim,), il, 0.0)]
-        plan += [
-            (p + "attn_output.weight", (E, cfg.q_dim), il, 0.02),
-            (p + cfg.ffn_norm_name, (E,), il, 0.0),
-        ]
-        if cfg.fused_qkv:
+        plan.append((p + "attn_output.weight", (E, cfg.q_dim), il, 0.02))
+        if all_bias:
+            plan.append((p + "attn_output.bias", (E,), il, 0.05))
+        if cfg.norm_type == "layer":
+            plan += norm(p + "ffn_norm", il, nl["ffn"])
+        else:
+            plan.append((p + cfg.ffn_norm_name, (E,), il, 0.0))
+        if cfg.ffn_act == "gelu":       # non-gated MLP
+            plan += [(p + "ffn_up.weight", (F, E), il, 0.02), (p + "ffn_down.weight", (E, F), il, 0.02)]
+            if all_bias:
+                plan += [(p + "ffn_up.bias", (F,), il, 0.05), (p + "ffn_down.bias", (E,), il, 0.05)]
+        elif cfg.fused_gate_up:
             plan += [(p + "ffn_up.weight", (2 * F, E), il, 0.02), (p + "ffn_down.weight", (E, F), il, 0.02)]
         elif cfg.is_moe:
             plan += [
@@ -158,7 +179,7 @@ def _tensor_plan(cfg: ModelConfig, rope_freqs: bool):
                 (p + "ffn_down.weight", (E, F), il, 0.02),
                 (p + "ffn_up.weight", (F, E), il, 0.02),
             ]
-    plan.append(("output_norm.weight", (E,), -1, 0.0))
+    plan += norm("output_norm", -1, nl["out"])
     if not cfg.tie_embeddings:
         plan.append(("output.weight", (cfg.vocab_size, E), -1, 0.02))
     return plan
@@ -183,7 +204,7 @@ def write_synthetic_gguf(path: str, cfg: ModelConfig, ftype: str = "F16", seed: 
     w.add(f"{a}.feed_forward_length", cfg.n_ff, ValueType.UINT32)
     w.add(f"{a}.attention.head_count", cfg.n_head, ValueType.UINT32)
     w.add(f"{a}.attention.head_count_kv", cfg.n_head_kv, ValueType.UINT32)
-    w.add(f"{a}.attention.layer_norm_rms_epsilon", float(cfg.rms_eps), ValueType.FLOAT32)
+    w.add(f"{a}.attention.layer_norm_epsilon" if cfg.norm_type == "layer" else f"{a}.attention.layer_norm_rms_epsilon", float(cfg.rms_eps), ValueType.FLOAT32)
     w.add(f"{a}.rope.freq_base", float(cfg.rope_theta), ValueType.FLOAT32)
     w.add(f"{a}.rope.dimension_count", cfg.rope_dim, ValueType.UINT32)
     if cfg.head_dim * cfg.n_head != cfg.n_embd:
@@ -193,8 +214,8 @@ def write_synthetic_gguf(path: str, cfg: ModelConfig, ftype: str = "F16", seed: 
         w.add(f"{a}.embedding_scale", float(cfg.embedding_scale), ValueType.FLOAT32)
     if cfg.residual_scale != 1.0:
         w.add(f"{a}.residual_scale", float(cfg.residual_scale), ValueType.FLOAT32)
-    if cfg.logit_scale != 1.0:
-        w.add(f"{a}.logit_scale", float(cfg.logit_scale), ValueType.FLOAT32)
+    if cfg.logit_scale != 1.0:      # command-r multiplies the logits by its key, the granite family divides by it
+        w.add(f"{a}.logit_scale", float(1.0 / cfg.logit_scale if a == "command-r" else cfg.logit_scale), ValueType.FLOAT32)
     if cfg.attention_scale > 0.0:
         w.add(f"{a}.attention.scale", float(cfg.attention_scale), ValueType.FLOAT32)
     if cfg.yarn_factor > 1.0:

@@ -51,6 +51,17 @@ class ModelConfig:
     # qwen2moe: routed experts without re-normalised top-k weights plus an always-on shared expert behind a sigmoid gate
     moe_norm_topk: bool = True     # renormalise the selected experts' weights (Mixtral, qwen3moe); qwen2moe: False
     n_ff_shared: int = 0           # > 0: shared-expert FFN width (`ffn_*_shexp`, gate vector `ffn_gate_inp_shexp`)
+    # LayerNorm / GELU / parallel-residual families (starcoder2, falcon, olmo, orion, command-r): the generic layer path
+    norm_type: str = "rms"         # "rms" | "layer" (mean-centred; weight and bias optional per file: olmo has neither)
+    ffn_act: str = "swiglu"        # "swiglu" (gated SiLU) | "gelu" (ffn_up -> GELU -> ffn_down, biases optional)
+    parallel_residual: bool = False  # h + attn(n(h)) + ffn(n'(h)) instead of the sequential form (falcon, command-r)
+    fused_gate_up: bool = False    # phi3: ffn_up holds [gate | up]
+
+    @property
+    def generic(self) -> bool:
+        """True for families that run the unfused layer path (models/llama.py `_layer_generic`)."""
+        return self.norm_type != "rms" or self.ffn_act != "swiglu" or self.parallel_residual
+
     # smollm3: every `no_rope_step`-th layer attends without rotary position encoding (`llama.cpp/src/models/smollm3.cpp:26`)
     no_rope_step: int = 0
 
@@ -145,7 +156,21 @@ PRESETS: dict[str, ModelConfig] = {
                                 head_dim=64, n_ff=512, n_ctx_train=512, rope_theta=10000.0, rope_dim=64, no_rope_step=4),
     "tiny-phi3": ModelConfig(name="tiny-phi3", arch="phi3", vocab_size=512, n_embd=256, n_layer=2, n_head=4, n_head_kv=4,
                              head_dim=64, n_ff=512, n_ctx_train=512, rope_theta=10000.0, rope_dim=64, rope_neox=True,
-                             fused_qkv=True),
+                             fused_qkv=True, fused_gate_up=True),
+    # LayerNorm families
+    "tiny-starcoder2": ModelConfig(name="tiny-starcoder2", arch="starcoder2", vocab_size=512, n_embd=256, n_layer=2, n_head=4, n_head_kv=2,
+                                   head_dim=64, n_ff=512, n_ctx_train=512, rope_theta=10000.0, rope_dim=64, rope_neox=True, qkv_bias=True,
+                                   norm_type="layer", ffn_act="gelu"),
+    "tiny-falcon": ModelConfig(name="tiny-falcon", arch="falcon", vocab_size=512, n_embd=256, n_layer=2, n_head=4, n_head_kv=1,
+                               head_dim=64, n_ff=1024, n_ctx_train=512, rope_theta=10000.0, rope_dim=64, rope_neox=True, fused_qkv=True,
+                               norm_type="layer", ffn_act="gelu", parallel_residual=True),
+    "tiny-olmo": ModelConfig(name="tiny-olmo", arch="olmo", vocab_size=512, n_embd=256, n_layer=2, n_head=4, n_head_kv=4,
+                             head_dim=64, n_ff=512, n_ctx_train=512, rope_theta=10000.0, rope_dim=64, norm_type="layer"),
+    "tiny-orion": ModelConfig(name="tiny-orion", arch="orion", vocab_size=512, n_embd=256, n_layer=2, n_head=4, n_head_kv=4,
+                              head_dim=64, n_ff=512, n_ctx_train=512, rope_theta=10000.0, rope_dim=64, rope_neox=True, norm_type="layer"),
+    "tiny-command-r": ModelConfig(name="tiny-command-r", arch="command-r", vocab_size=512, n_embd=256, n_layer=2, n_head=4, n_head_kv=2,
+                                  head_dim=64, n_ff=512, n_ctx_train=512, rope_theta=10000.0, rope_dim=64, norm_type="layer",
+                                  parallel_residual=True, logit_scale=16.0, tie_embeddings=True),
     "qwen2.5-7b": ModelConfig(name="qwen2.5-7b", arch="qwen2", vocab_size=152064, n_embd=3584, n_layer=28, n_head=28,
                               n_head_kv=4, head_dim=128, n_ff=18944, n_ctx_train=32768, rms_eps=1e-6, rope_theta=1000000.0,
                               rope_dim=128, rope_neox=True, qkv_bias=True, bos_id=151643, eos_id=151645),
@@ -180,8 +205,13 @@ PRESETS: dict[str, ModelConfig] = {
 #   internlm2, xverse, ernie4_5 - none (adjacent-pair rotation);   exaone, seed_oss - half-split rotation (seed_oss: optional QKV bias);
 #   minicpm, granitemoe - the granite builder (four scalars; granitemoe with routed experts);   smollm3 - no rotation on every 4th layer.
 SUPPORTED_ARCHS = {"llama", "qwen2", "qwen2moe", "qwen3", "qwen3moe", "phi3", "granite",
-                   "internlm2", "xverse", "ernie4_5", "exaone", "seed_oss", "minicpm", "granitemoe", "smollm3"}
-ROPE_NORM_ARCHS = {"llama", "granite", "granitemoe", "minicpm", "internlm2", "xverse", "ernie4_5", "smollm3"}     # llama_model_rope_type
+                   "internlm2", "xverse", "ernie4_5", "exaone", "seed_oss", "minicpm", "granitemoe", "smollm3",
+                   "starcoder2", "falcon", "olmo", "orion", "command-r"}
+ROPE_NORM_ARCHS = {"llama", "granite", "granitemoe", "minicpm", "internlm2", "xverse", "ernie4_5", "smollm3", "olmo", "command-r"}     # llama_model_rope_type
+# LayerNorm families and what differs beyond the norm (llama.cpp/src/models/{starcoder2,falcon,olmo,orion,command-r}.cpp):
+#   starcoder2: biases on every matrix, non-gated GELU MLP;  falcon: fused QKV, GELU MLP, attention and MLP in parallel from the same
+#   (or a second) norm;  olmo: norms without parameters;  orion: llama with LayerNorm;  command-r: parallel, logits * logit_scale
+LAYERNORM_ARCHS = {"starcoder2", "falcon", "olmo", "orion", "command-r"}
 
 
 def preset(name: str, **overrides) -> ModelConfig:
@@ -223,6 +253,9 @@ def config_from_gguf(meta: dict[str, Any], tensors: dict | None = None) -> Model
                     yarn_beta_fast=float(g("rope.scaling.yarn_beta_fast", 32.0)), yarn_beta_slow=float(g("rope.scaling.yarn_beta_slow", 1.0)))
     tie = tensors is not None and "output.weight" not in tensors
     n_layer = int(g("block_count"))
+    if tensors is not None and "blk.0.ffn_down.weight" in tensors and int(g("feed_forward_length")) != tensors["blk.0.ffn_down.weight"].shape[-1]:
+        raise ValueError(f"{arch}.feed_forward_length = {g('feed_forward_length')} but blk.0.ffn_down.weight has {tensors['blk.0.ffn_down.weight'].shape[-1]} "
+                         "input columns: the file's metadata does not describe its tensors")
     # minicpm: defaults of older exports (llama-model.cpp:756-770), overridden by the keys when present
     dflt = dict(embedding_scale=12.0, residual_scale=1.4 / math.sqrt(n_layer), logit_scale=256.0 / n_embd) if arch == "minicpm" else \
         dict(embedding_scale=1.0, residual_scale=1.0, logit_scale=1.0)
@@ -231,10 +264,12 @@ def config_from_gguf(meta: dict[str, Any], tensors: dict | None = None) -> Model
         n_layer=int(g("block_count")), n_head=n_head, n_head_kv=n_head_kv, head_dim=head_dim,
         n_ff=int(g("expert_feed_forward_length") or g("feed_forward_length")) if int(g("expert_count", 0) or 0) > 0 else int(g("feed_forward_length")),
         n_ctx_train=int(g("context_length", 2048)),
-        rms_eps=float(g("attention.layer_norm_rms_epsilon", 1e-5)), rope_theta=float(g("rope.freq_base", 10000.0)),
+        rms_eps=float(g("attention.layer_norm_epsilon", 1e-5) if arch in LAYERNORM_ARCHS else g("attention.layer_norm_rms_epsilon", 1e-5)),
+        norm_type="layer" if arch in LAYERNORM_ARCHS else "rms", ffn_act="gelu" if arch in ("starcoder2", "falcon") else "swiglu",
+        parallel_residual=arch in ("falcon", "command-r"), fused_gate_up=arch == "phi3", rope_theta=float(g("rope.freq_base", 10000.0)),
         rope_dim=int(g("rope.dimension_count", head_dim)), rope_neox=arch not in ROPE_NORM_ARCHS, rope_scale_linear=scale,
         embedding_scale=float(g("embedding_scale") or dflt["embedding_scale"]), residual_scale=float(g("residual_scale") or dflt["residual_scale"]),
-        logit_scale=float(g("logit_scale") or dflt["logit_scale"]), attention_scale=float(g("attention.scale", 0.0) or 0.0),
+        logit_scale=(1.0 / float(g("logit_scale") or 1.0)) if arch == "command-r" else float(g("logit_scale") or dflt["logit_scale"]), attention_scale=float(g("attention.scale", 0.0) or 0.0),
         no_rope_step=4 if arch == "smollm3" else 0,
         moe_norm_topk=arch != "qwen2moe", n_ff_shared=int(g("expert_shared_feed_forward_length", 0) or 0),
         qkv_bias=arch in ("qwen2", "qwen2moe") or (tensors is not None and "blk.0.attn_q.bias" in tensors),

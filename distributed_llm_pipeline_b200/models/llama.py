@@ -116,6 +116,10 @@ class LlamaEngine:
         qkv_dim = (self.Hq + 2 * self.Hkv) * self.D
         self.h = torch.zeros(M, self.E, dtype=f32, device=dev)
         self.fused_tp = bool(getattr(self.comm, "fused", False)) and self.comm.tp_size > 1 and not cfg.is_moe
+        if cfg.generic and self.fused_tp:
+            raise NotImplementedError(f"the {cfg.arch} family runs the generic layer path: tensor parallelism through --tp-impl nccl")
+        if cfg.generic and cfg.is_moe:
+            raise NotImplementedError("routed experts are not implemented on the generic layer path")
         self.sp_ok = False
         self._greedy_now = False
         if self.fused_tp:
@@ -137,6 +141,9 @@ class LlamaEngine:
         self.q = torch.zeros(M, self.Hq * self.D, dtype=f16, device=dev)
         self.att = torch.zeros(M, self.Hq * self.D, dtype=f16, device=dev)
         self.act = torch.zeros(M, self.F, dtype=f16, device=dev)
+        # generic layer path: fp32 MLP pre-activation (bias + GELU run between the two mat-muls), second norm output (falcon-40b)
+        self.up32 = torch.zeros(M, self.F, dtype=f32, device=dev) if cfg.ffn_act != "swiglu" else None
+        self.xn2 = torch.zeros(M, self.E, dtype=f16, device=dev) if any(lw.attn_norm2 is not None for lw in weights.layers.values()) else None
         self.tokens = torch.zeros(M, dtype=i32, device=dev)
         self.pos = torch.zeros(M, dtype=i32, device=dev)
         self.slot = torch.zeros(M, dtype=i32, device=dev)
@@ -340,6 +347,50 @@ class LlamaEngine:
         else:
             ops.linear(lw.w_down, act, "add", out=h, scratch=self._scratch_for(lw.w_down))
 
+    def _norm(self, h, w, b, delta=None, out=None):
+        if self.cfg.norm_type == "layer":
+            return ops.layernorm(h, w, b, self.cfg.rms_eps, delta=delta, out=out)
+        return ops.rmsnorm(h, w, self.cfg.rms_eps, delta=delta, out=out)
+
+    def _layer_generic(self, il: int, T: int, attn_fn):
+        """LayerNorm / GELU / parallel-residual families (starcoder2, falcon, olmo, orion, command-r; `build_norm` LLM_NORM,
+        `build_ffn` LLM_FFN_GELU + LLM_FFN_SEQ in llama-graph.cpp:785-990): the same mat-vec / GEMM / attention kernels as `_layer`
+        with the norm, the bias + activation and the residual adds as separate launches instead of fused prologues / epilogues."""
+        lw, cfg, comm = self.w.layers[il], self.cfg, self.comm
+        h = self.h[:T]
+        tp = comm.tp_size > 1
+        xn = self._norm(h, lw.attn_norm, lw.attn_norm_b, out=self.xn[:T])
+        xa = self._norm(h, lw.attn_norm2, lw.attn_norm2_b, out=self.xn2[:T]) if lw.attn_norm2 is not None else xn
+        qkv = self.qkv16[:T]
+        if lw.wv is None:
+            ops.linear(lw.wqkv, xa, "f16", out=qkv, scratch=self._scratch_for(lw.wqkv))
+        else:
+            ops.linear(lw.wqkv, xa, "f16", out=qkv[:, :lw.wqkv.N], scratch=self._scratch_for(lw.wqkv))
+            ops.linear(lw.wv, xa, "f16", out=qkv[:, lw.wqkv.N:], scratch=self._scratch_for(lw.wv))
+        q = self._rope(il, qkv, T)
+        att = attn_fn(il, q, T)
+        d = ops.linear(lw.wo, att, "f32", out=self.delta[:T], scratch=self._scratch_for(lw.wo))
+        if tp:
+            d = comm.allreduce_delta(d, il, 0)
+        if lw.bo is not None:
+            d.add_(lw.bo)
+        if cfg.parallel_residual:       # the MLP reads the norm of the block INPUT: add the attention branch to h only now
+            h.add_(d)
+            ffn_in = xn
+        else:
+            ffn_in = self._norm(h, lw.ffn_norm, lw.ffn_norm_b, delta=d, out=self.xn[:T])       # h += d inside
+        if cfg.ffn_act == "gelu":
+            up = ops.linear(lw.w_up, ffn_in, "f32", out=self.up32[:T], scratch=self._scratch_for(lw.w_up))
+            act = ops.bias_act(up, lw.b_up, "gelu", out=self.act[:T])
+        else:
+            act = ops.linear(lw.w_gate, ffn_in, "swiglu", w_up=lw.w_up, out=self.act[:T], scratch=self._scratch_for(lw.w_gate, lw.w_up))
+        d = ops.linear(lw.w_down, act, "f32", out=self.delta[:T], scratch=self._scratch_for(lw.w_down))
+        if tp:
+            d = comm.allreduce_delta(d, il, 1)
+        h.add_(d)
+        if lw.b_down is not None:
+            h.add_(lw.b_down)
+
     def _layer_fused(self, il: int, T: int, attn_fn):
         """Decode layer with the tensor-parallel all-reduces fused into the mat-vecs (parallel/fused.py):
         row-parallel GEMVs push partial rows into every peer's reduce buffer, the following GEMV's prologue
@@ -511,8 +562,9 @@ class LlamaEngine:
             for il in self.w.layer_range:
                 self._layer_fused(il, T, attn_fn)
             return
+        layer = self._layer_generic if self.cfg.generic else self._layer
         for il in self.w.layer_range:
-            self._layer(il, T, attn_fn)
+            layer(il, T, attn_fn)
             if il in self.cvec:                     # control vector: h += direction[il] (llama-adapter.cpp apply_to)
                 self.h[:T].add_(self.cvec[il])
             if self.eval_callback is not None:      # tensor inspection hook (ggml-backend.cpp:1584-1616, examples/eval-callback)
@@ -623,10 +675,10 @@ class LlamaEngine:
         """logits for `n` rows of h (already gathered to the front of the xn buffer) -> self.logits[:n]."""
         cfg = self.cfg
         hsel = self.h[rows]
-        if n <= 4 and n != 3:
+        if n <= 4 and n != 3 and cfg.norm_type == "rms":
             lg = ops.linear(self.w.lm_head, hsel.contiguous(), "f32", norm_w=self.w.out_norm, eps=cfg.rms_eps, out=self.logits[:n])
         else:
-            xn = ops.rmsnorm(hsel.contiguous(), self.w.out_norm, cfg.rms_eps)
+            xn = self._norm(hsel.contiguous(), self.w.out_norm, self.w.out_norm_b)
             lg = ops.linear(self.w.lm_head, xn, "f32", out=self.logits[:n], scratch=self._scratch_for(self.w.lm_head))
         return self.comm.allgather_logits(lg, self.w.vocab_range, cfg.vocab_size)
 
@@ -677,7 +729,7 @@ class LlamaEngine:
         if all_logits:
             if n > chunk:
                 raise ValueError("all_logits needs the tokens to fit one chunk")
-            xn = ops.rmsnorm(self.h[:T], self.w.out_norm, self.cfg.rms_eps)
+            xn = self._norm(self.h[:T], self.w.out_norm, self.w.out_norm_b)
             lg = ops.linear(self.w.lm_head, xn, "f32", scratch=self._scratch_for(self.w.lm_head))
             return self.comm.allgather_logits(lg, self.w.vocab_range, self.cfg.vocab_size)
         return self._head(slice(T - 1, T), 1)[0]
@@ -704,7 +756,7 @@ class LlamaEngine:
             self.tokens[:T].copy_(torch.as_tensor(tokens, dtype=torch.int32))
             self._embed(T)
             self._run_layers(T, self._attn_prefill_for(sid, 0))
-            xn = ops.rmsnorm(self.h[:T], self.w.out_norm, self.cfg.rms_eps).float()
+            xn = self._norm(self.h[:T], self.w.out_norm, self.w.out_norm_b).float()
         finally:
             self.free_seq(sid)
         if pooling == "mean":

@@ -106,6 +106,13 @@ class ReferenceModel:
             y = y + scale * ((x @ a.T) @ b.T)
         return y
 
+    def norm(self, x: torch.Tensor, name: str) -> torch.Tensor:
+        """RMSNorm, or for the LayerNorm families the mean-centred norm with whatever of `<name>.weight` / `.bias` the file has."""
+        c, w = self.cfg, self.w
+        if c.norm_type == "layer":
+            return torch.nn.functional.layer_norm(x, (x.shape[-1],), w.get(name + ".weight"), w.get(name + ".bias"), c.rms_eps)
+        return rms_norm(x, w[name + ".weight"], c.rms_eps)
+
     def layer_inv_freq(self, il: int) -> torch.Tensor:
         return self.inv_freq if self.cfg.layer_uses_rope(il) else self.inv_freq_off
 
@@ -153,12 +160,19 @@ class ReferenceModel:
         scores = scores.masked_fill(mask[None], float("-inf"))
         att = torch.softmax(scores, dim=-1)
         o = torch.einsum("hts,shd->thd", att, Vx).reshape(T, c.q_dim)
-        return self.mm(o, p + "attn_output.weight")
+        out = self.mm(o, p + "attn_output.weight")
+        return out + w[p + "attn_output.bias"] if p + "attn_output.bias" in w else out
 
     def ffn(self, il: int, x: torch.Tensor) -> torch.Tensor:
         c, w = self.cfg, self.w
         p = f"blk.{il}."
-        if c.fused_qkv:   # phi3: ffn_up holds [gate | up]; swiglu = silu(first half) * second half
+        if c.ffn_act == "gelu":   # non-gated MLP with optional biases (starcoder2, falcon); GELU in its tanh form, as ggml computes it
+            up = self.mm(x, p + "ffn_up.weight")
+            if p + "ffn_up.bias" in w:
+                up = up + w[p + "ffn_up.bias"]
+            dn = self.mm(torch.nn.functional.gelu(up, approximate="tanh"), p + "ffn_down.weight")
+            return dn + w[p + "ffn_down.bias"] if p + "ffn_down.bias" in w else dn
+        if c.fused_gate_up:   # phi3: ffn_up holds [gate | up]; swiglu = silu(first half) * second half
             g, u = self.mm(x, p + "ffn_up.weight").split([c.n_ff, c.n_ff], dim=-1)
             return self.mm(torch.nn.functional.silu(g) * u, p + "ffn_down.weight")
         if not c.is_moe:
@@ -192,8 +206,12 @@ class ReferenceModel:
     def layer(self, il: int, h: torch.Tensor, pos: torch.Tensor, cache: RefKVCache) -> torch.Tensor:
         c, w = self.cfg, self.w
         p = f"blk.{il}."
-        h = h + c.residual_scale * self.attention(il, rms_norm(h, w[p + "attn_norm.weight"], c.rms_eps), pos, cache)
-        h = h + c.residual_scale * self.ffn(il, rms_norm(h, w[p + c.ffn_norm_name], c.rms_eps))
+        if c.parallel_residual:     # falcon, command-r: both branches read the block input (falcon-40b: through two different norms)
+            xn = self.norm(h, p + "attn_norm")
+            xa = self.norm(h, p + "attn_norm_2") if p + "attn_norm_2.weight" in w else xn
+            return h + self.attention(il, xa, pos, cache) + self.ffn(il, xn)
+        h = h + c.residual_scale * self.attention(il, self.norm(h, p + "attn_norm"), pos, cache)
+        h = h + c.residual_scale * self.ffn(il, self.norm(h, p + c.ffn_norm_name[: -len(".weight")]))
         return h
 
     def embed(self, tokens: torch.Tensor) -> torch.Tensor:
@@ -202,7 +220,7 @@ class ReferenceModel:
     def head(self, h: torch.Tensor) -> torch.Tensor:
         c, w = self.cfg, self.w
         out_w = w.get("output.weight", w["token_embd.weight"])
-        xn = rms_norm(h, w["output_norm.weight"], c.rms_eps)
+        xn = self.norm(h, "output_norm")
         if self.observer is not None:
             self.observer("output.weight" if "output.weight" in w else "token_embd.weight", xn, None)
         return xn @ out_w.T / c.logit_scale

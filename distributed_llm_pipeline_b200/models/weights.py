@@ -45,6 +45,14 @@ class LayerWeights:
     e_down_s: DeviceWeight | None = None
     router_w: DeviceWeight | None = None
     router_wp: DeviceWeight | None = None              # router_w zero-padded to a multiple of 128 rows
+    # LayerNorm / biased families (generic layer path): every one optional
+    attn_norm_b: torch.Tensor | None = None
+    ffn_norm_b: torch.Tensor | None = None
+    attn_norm2: torch.Tensor | None = None             # falcon-40b: the attention branch has its own norm
+    attn_norm2_b: torch.Tensor | None = None
+    bo: torch.Tensor | None = None                     # fp32 [E] attention output bias (added once, after the TP reduction)
+    b_up: torch.Tensor | None = None                   # fp32 [local F]
+    b_down: torch.Tensor | None = None                 # fp32 [E]
 
 
 @dataclass
@@ -62,6 +70,7 @@ class ModelWeights:
     n_head_local: int = 0
     n_head_kv_local: int = 0
     n_ff_local: int = 0
+    out_norm_b: torch.Tensor | None = None
 
     def nbytes(self) -> int:
         tot = 0
@@ -206,15 +215,32 @@ def load_weights(src: str | GGUFModelFiles, device, layer_range: range | None = 
             dense = torch.cat([d.float() for d in dt], 0)
             wqkv = (DeviceWeight(GGMLType.F16, dense.shape[0], dense.shape[1], [], dense) if dev.type == "cpu"
                     else DeviceWeight(GGMLType.F16, dense.shape[0], dense.shape[1], [dense.to(torch.float16).contiguous()]))
-        lw = LayerWeights(attn_norm=f32(p + "attn_norm.weight"), wqkv=wqkv, wv=wv_sep,
-                          wo=mat(p + "attn_output.weight", cols=(hq0 * D, hq1 * D), scale=cfg.residual_scale), ffn_norm=f32(p + cfg.ffn_norm_name))
+        def norm_w(name):      # LayerNorm files may carry no weight (olmo) or no such norm at all (parallel blocks): ones / None
+            if name in f:
+                return f32(name)
+            return torch.ones(cfg.n_embd, dtype=torch.float32, device=dev) if cfg.norm_type == "layer" else None
+
+        def opt(name):
+            return f32(name) if name in f else None
+        lw = LayerWeights(attn_norm=norm_w(p + "attn_norm.weight"), wqkv=wqkv, wv=wv_sep,
+                          wo=mat(p + "attn_output.weight", cols=(hq0 * D, hq1 * D), scale=cfg.residual_scale),
+                          ffn_norm=None if (cfg.parallel_residual and p + cfg.ffn_norm_name not in f) else norm_w(p + cfg.ffn_norm_name))
+        if cfg.generic:
+            lw.attn_norm_b, lw.ffn_norm_b = opt(p + "attn_norm.bias"), opt(p + "ffn_norm.bias")
+            lw.attn_norm2, lw.attn_norm2_b = opt(p + "attn_norm_2.weight"), opt(p + "attn_norm_2.bias")
+            lw.bo, lw.b_down = opt(p + "attn_output.bias"), opt(p + "ffn_down.bias")
         if cfg.qkv_bias:
             lw.qkv_bias = torch.cat([f32(p + "attn_q.bias")[qr[0]:qr[1]], f32(p + "attn_k.bias")[kr[0]:kr[1]],
                                      f32(p + "attn_v.bias")[kr[0]:kr[1]]]).contiguous()
         if cfg.qk_norm:
             lw.q_norm, lw.k_norm = f32(p + "attn_q_norm.weight"), f32(p + "attn_k_norm.weight")
         f0, f1 = _split(cfg.n_ff, tp_size, tp_rank, 256 if tp_size > 1 else 1)
-        if cfg.fused_qkv:   # phi3: ffn_up rows [gate | up]
+        if cfg.ffn_act == "gelu":     # non-gated MLP: up -> GELU -> down
+            lw.w_up = mat(p + "ffn_up.weight", rows=(f0, f1))
+            lw.w_down = mat(p + "ffn_down.weight", cols=(f0, f1), scale=cfg.residual_scale)
+            if p + "ffn_up.bias" in f:
+                lw.b_up = f32(p + "ffn_up.bias")[f0:f1].contiguous()
+        elif cfg.fused_gate_up:   # phi3: ffn_up rows [gate | up]
             lw.w_gate = mat(p + "ffn_up.weight", rows=(f0, f1))
             lw.w_up = mat(p + "ffn_up.weight", rows=(cfg.n_ff + f0, cfg.n_ff + f1))
             lw.w_down = mat(p + "ffn_down.weight", cols=(f0, f1), scale=cfg.residual_scale)
@@ -252,14 +278,16 @@ def load_weights(src: str | GGUFModelFiles, device, layer_range: range | None = 
         layers[il] = lw
 
     tok = mat("token_embd.weight") if first_stage else None
-    out_norm = lm = None
+    out_norm = out_norm_b = lm = None
     v0, v1 = 0, cfg.vocab_size
     if last_stage:
-        out_norm = f32("output_norm.weight") / cfg.logit_scale      # granite: logits / logit_scale, folded into the final norm
+        # granite: logits / logit_scale, folded into the final norm (weight and, for LayerNorm files, bias)
+        out_norm = (f32("output_norm.weight") if "output_norm.weight" in f else torch.ones(cfg.n_embd, dtype=torch.float32, device=dev)) / cfg.logit_scale
+        out_norm_b = f32("output_norm.bias") / cfg.logit_scale if "output_norm.bias" in f else None
         name = "output.weight" if "output.weight" in f else "token_embd.weight"
         if shard_vocab and tp_size > 1 and cfg.vocab_size % (2 * tp_size) == 0:
             v0, v1 = _split(cfg.vocab_size, tp_size, tp_rank)
         lm = mat(name, rows=(v0, v1))
     freqs = f32("rope_freqs.weight") if "rope_freqs.weight" in f else None
     return ModelWeights(cfg, layers, layer_range, tp_rank, tp_size, tok, out_norm, lm, (v0, v1), freqs,
-                        n_head_local=hq1 - hq0, n_head_kv_local=n_kv_local, n_ff_local=cfg.n_ff // tp_size)
+                        n_head_local=hq1 - hq0, n_head_kv_local=n_kv_local, n_ff_local=cfg.n_ff // tp_size, out_norm_b=out_norm_b)

@@ -81,6 +81,41 @@ def rmsnorm(h: torch.Tensor, w: torch.Tensor, eps: float, delta: torch.Tensor | 
     return out
 
 
+def layernorm(h: torch.Tensor, w: torch.Tensor | None, b: torch.Tensor | None, eps: float, delta: torch.Tensor | None = None,
+              out: torch.Tensor | None = None) -> torch.Tensor:
+    """h (fp32 [T,E], updated in place with += delta) -> fp16 LayerNorm(h) * w + b (either may be None)."""
+    T, E = h.shape
+    if out is None:
+        out = torch.empty(T, E, dtype=torch.float16, device=h.device)
+    if not native(h):
+        if delta is not None:
+            h.add_(delta)
+        out.copy_(torch.nn.functional.layer_norm(h, (E,), w, b, eps).to(torch.float16))
+        return out
+    _lib.check(_lib.load().dlp_layernorm(h.data_ptr(), _p(delta), _p(w), _p(b), out.data_ptr(), T, E, eps, _stream()), "layernorm")
+    _count()
+    return out
+
+
+ACTS = {"none": 0, "gelu": 1, "relu2": 2, "silu": 3, "gelu_erf": 4}
+
+
+def bias_act(x: torch.Tensor, bias: torch.Tensor | None, act: str, out: torch.Tensor | None = None) -> torch.Tensor:
+    """fp16 act(x + bias) for fp32 x [T, F]: the step between the two mat-muls of a non-gated MLP."""
+    T, F = x.shape
+    if out is None:
+        out = torch.empty(T, F, dtype=torch.float16, device=x.device)
+    if not native(x) or x.dtype != torch.float32:
+        v = x.float() + (bias if bias is not None else 0.0)
+        fn = {"none": lambda t: t, "gelu": lambda t: torch.nn.functional.gelu(t, approximate="tanh"), "relu2": lambda t: torch.relu(t) ** 2,
+              "silu": torch.nn.functional.silu, "gelu_erf": torch.nn.functional.gelu}[act]
+        out.copy_(fn(v).to(torch.float16))
+        return out
+    _lib.check(_lib.load().dlp_bias_act(x.data_ptr(), _p(bias), out.data_ptr(), T, F, ACTS[act], _stream()), "bias_act")
+    _count()
+    return out
+
+
 def _linear_cpu(w, x, w_up, norm_w, eps, out, mode):
     xf = x.float()
     if norm_w is not None:

@@ -50,6 +50,8 @@ def _declare(lib):
         "dlp_dequant_rows_f32": (i32, [W, vp, i32, vp, i32, vp]),
         "dlp_dequant_rows_f16": (i32, [W, vp, i32, vp, i32, vp]),
         "dlp_rmsnorm": (i32, [vp, vp, vp, vp, i32, i32, f32, vp]),
+        "dlp_layernorm": (i32, [vp, vp, vp, vp, vp, i32, i32, f32, vp]),
+        "dlp_bias_act": (i32, [vp, vp, vp, i32, i32, i32, vp]),
         "dlp_rope_kv": (i32, [vp, i32, vp, vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, i32, i32, f32, vp]),
         "dlp_rope_kv_ex": (i32, [vp, i32, vp, vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, i32, i32, f32, vp, vp, vp, f32,
                                  vp, C.c_size_t, vp, C.c_size_t, vp]),

@@ -85,6 +85,12 @@ int dlp_dequant_rows_f16(const dlp_weight* w, const int32_t* row_ids, int n_rows
 /* h[T,E] (fp32) += delta (optional, fp32); out (fp16, optional) = RMSNorm(h) * w.   ref: rms_norm_f32 fused mul+add (norm.cu:107). */
 int dlp_rmsnorm(float* h, const float* delta, const float* w, void* out_f16, int T, int E, float eps, void* stream);
 
+/* LayerNorm families: h[T,E] (fp32) += delta (optional); out (fp16, optional) = (h - mean) * rsqrt(var + eps) * w + b, w and b optional.
+ * ref: norm_f32 (norm.cu:5-45) + the mul / add nodes of build_norm (llama-graph.cpp:785). */
+int dlp_layernorm(float* h, const float* delta, const float* w, const float* b, void* out_f16, int T, int E, float eps, void* stream);
+/* out fp16 [T,F] = act(x fp32 [T,F] + bias[F] (optional)); act: 0 none, 1 GELU (tanh), 2 ReLU^2, 3 SiLU, 4 GELU (erf).  ref: unary.cu. */
+int dlp_bias_act(const float* x, const float* bias, void* out_f16, int T, int F, int act, void* stream);
+
 /* RoPE on Q,K + paged KV write of K,V.  qkv [T,(Hq+2Hkv)*D] fp32/fp16; q_out fp16 [T,Hq*D] scaled by q_scale;
  * caches [n_pages][Hkv][page_size][D] fp16; slot[t] = page*page_size+offset (<0: no write).
  * ref: rope_norm/rope_neox with fused set_rows (rope.cu:44-111,58-78), k_set_rows (set-rows.cu). */

@@ -40,6 +40,14 @@ CASES = {
     "granitemoe": ("GraniteMoeConfig", "GraniteMoeForCausalLM", {"intermediate_size": 256, "num_local_experts": 4, "num_experts_per_tok": 2,
                                                                  "embedding_multiplier": 12.0, "residual_multiplier": 0.22, "logits_scaling": 8.0,
                                                                  "attention_multiplier": 0.015625}),
+    "starcoder2": ("Starcoder2Config", "Starcoder2ForCausalLM", {"norm_epsilon": 1e-5, "use_bias": True, "hidden_act": "gelu_pytorch_tanh", "sliding_window": None,
+                                                                 "tie_word_embeddings": True}),
+    "falcon": ("FalconConfig", "FalconForCausalLM", {"multi_query": True, "new_decoder_architecture": False, "parallel_attn": True, "bias": False, "alibi": False,
+                                                     "num_kv_heads": None, "activation": "gelu_pytorch_tanh", "tie_word_embeddings": False, "ffn_hidden_size": 1024}),
+    "falcon-new-arch": ("FalconConfig", "FalconForCausalLM", {"multi_query": False, "new_decoder_architecture": True, "parallel_attn": True, "bias": False, "alibi": False,
+                                                              "num_kv_heads": 2, "activation": "gelu_pytorch_tanh", "tie_word_embeddings": False, "ffn_hidden_size": 1024}),
+    "olmo": ("OlmoConfig", "OlmoForCausalLM", {"clip_qkv": None, "num_key_value_heads": 4}),
+    "command-r": ("CohereConfig", "CohereForCausalLM", {"logit_scale": 0.0625, "layer_norm_eps": 1e-5, "use_qk_norm": False, "tie_word_embeddings": True}),
     "qwen3moe": ("Qwen3MoeConfig", "Qwen3MoeForCausalLM", {"head_dim": 64, "moe_intermediate_size": 128, "num_experts": 4,
                                                              "num_experts_per_tok": 2, "norm_topk_prob": True}),
 }
@@ -70,7 +78,7 @@ def test_converted_model_matches_hf_forward(tmp_path, family):
     with torch.no_grad():
         want = model(torch.tensor([ids])).logits[0]
     ref = ReferenceModel.from_gguf(out)
-    assert ref.cfg.arch == ("llama" if family in ("llama", "llama31", "mistral", "mixtral") else family.split("-")[0])
+    assert ref.cfg.arch == ("llama" if family in ("llama", "llama31", "mistral", "mixtral") else "command-r" if family == "command-r" else family.split("-")[0])
     if family == "qwen2-yarn":
         assert ref.cfg.yarn_factor == 4.0 and ref.cfg.yarn_orig_ctx == 128
     if family == "llama31":

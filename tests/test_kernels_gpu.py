@@ -165,6 +165,35 @@ def test_rmsnorm_with_residual():
     assert torch.allclose(h, ref_h, atol=1e-6) and nmse(ref, out) < 1e-6
 
 
+@pytest.mark.parametrize("affine", ["wb", "w", "none"])
+@pytest.mark.parametrize("T,E", [(1, 256), (7, 1024), (130, 6144)])
+def test_layernorm_with_residual(affine, T, E):
+    """LayerNorm of the starcoder2 / falcon / olmo / orion / command-r families against torch in fp32: with weight and bias, weight
+    only, and no parameters; the residual add into h included."""
+    h = torch.randn(T, E, device=DEV) * 2 + 0.5          # non-zero mean: the centring matters
+    d = torch.randn(T, E, device=DEV)
+    w = (torch.rand(E, device=DEV) + 0.5) if affine != "none" else None
+    b = torch.randn(E, device=DEV) * 0.1 if affine == "wb" else None
+    ref_h = h + d
+    ref = torch.nn.functional.layer_norm(ref_h, (E,), w, b, 1e-5)
+    out = ops.layernorm(h, w, b, 1e-5, delta=d)
+    assert torch.allclose(h, ref_h, atol=1e-6) and nmse(ref, out) < 1e-6
+    h2 = ref_h.clone()
+    assert nmse(ref, ops.layernorm(h2, w, b, 1e-5)) < 1e-6 and torch.equal(h2, ref_h)      # without delta h is left alone
+
+
+@pytest.mark.parametrize("act", ["gelu", "gelu_erf", "relu2", "silu", "none"])
+def test_bias_act(act):
+    """Bias + activation between the two mat-muls of a non-gated MLP, against torch in fp32."""
+    T, F = 9, 1536
+    x = torch.randn(T, F, device=DEV) * 3
+    bias = torch.randn(F, device=DEV)
+    fn = {"none": lambda t: t, "gelu": lambda t: torch.nn.functional.gelu(t, approximate="tanh"), "relu2": lambda t: torch.relu(t) ** 2,
+          "silu": torch.nn.functional.silu, "gelu_erf": torch.nn.functional.gelu}[act]
+    assert nmse(fn(x + bias), ops.bias_act(x, bias, act)) < 1e-6
+    assert nmse(fn(x), ops.bias_act(x, None, act)) < 1e-6
+
+
 @pytest.mark.parametrize("neox", [False, True])
 @pytest.mark.parametrize("D", [64, 128])
 def test_rope_kv_write(neox, D):

@@ -89,7 +89,10 @@ CASES = [("tiny", "F16", 4e-3, 8e-4), ("tiny", "Q8_0", 5e-2, 8e-3), ("tiny", "Q4
          # the llama graph under other architecture names (each loaded and run by the reference's own builder for that name)
          ("tiny-internlm2", "F16", 4e-3, 8e-4), ("tiny-xverse", "F16", 4e-3, 8e-4), ("tiny-ernie", "F16", 4e-3, 8e-4), ("tiny-exaone", "F16", 4e-3, 8e-4),
          ("tiny-seed-oss", "F16", 4e-3, 8e-4), ("tiny-minicpm", "F16", 4e-3, 8e-4), ("tiny-granitemoe", "F16", 4e-3, 8e-4),
-         ("tiny-smollm3", "F16", 4e-3, 8e-4)]
+         ("tiny-smollm3", "F16", 4e-3, 8e-4),
+         # LayerNorm families (norm with / without weight and bias, non-gated GELU MLP with biases, parallel residual, fused QKV)
+         ("tiny-starcoder2", "F16", 4e-3, 8e-4), ("tiny-starcoder2", "Q8_0", 5e-2, 8e-3), ("tiny-falcon", "F16", 4e-3, 8e-4), ("tiny-olmo", "F16", 4e-3, 8e-4),
+         ("tiny-orion", "F16", 4e-3, 8e-4), ("tiny-command-r", "F16", 4e-3, 8e-4)]
 
 
 @pytest.mark.parametrize("name,ftype,tol_max,tol_mean", CASES, ids=[f"{n}-{f}" for n, f, _, _ in CASES])

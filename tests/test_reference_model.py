@@ -64,7 +64,10 @@ def test_rope_modes():
 @pytest.mark.parametrize("key", [("tiny-qwen2", "F16"), ("tiny-qwen2", "Q8_0"), ("tiny-qwen3", "F16"), ("tiny-phi3", "F16"),
                                  ("tiny-phi3", "Q8_0"), ("tiny-qwen3moe", "F16"), ("tiny-qwen2moe", "F16"), ("tiny-granite", "F16"), ("tiny-granite", "Q8_0"),
                                  ("tiny-granite", "Q4_K_M"), ("tiny-internlm2", "F16"), ("tiny-xverse", "F16"), ("tiny-ernie", "F16"), ("tiny-exaone", "F16"),
-                                 ("tiny-seed-oss", "F16"), ("tiny-minicpm", "F16"), ("tiny-granitemoe", "F16"), ("tiny-smollm3", "F16"), ("tiny-smollm3", "Q8_0")])
+                                 ("tiny-seed-oss", "F16"), ("tiny-minicpm", "F16"), ("tiny-granitemoe", "F16"), ("tiny-smollm3", "F16"), ("tiny-smollm3", "Q8_0"),
+                                 # LayerNorm / GELU / parallel-residual families: the generic layer path
+                                 ("tiny-starcoder2", "F16"), ("tiny-starcoder2", "Q8_0"), ("tiny-falcon", "F16"), ("tiny-falcon", "Q8_0"), ("tiny-olmo", "F16"),
+                                 ("tiny-orion", "F16"), ("tiny-command-r", "F16")])
 def test_other_architectures_match_oracle_cpu(tmp_models, key):
     """qwen2 (QKV bias), qwen3 (per-head Q/K norm) and phi3 (fused QKV / gate-up tensors), all with half-split RoPE:
     engine (CPU op fallbacks, paged KV) against the fp32 oracle."""

@@ -24,10 +24,12 @@ from distributed_llm_pipeline_b200.gguf.synth import synthetic_vocab  # noqa: E4
 
 ARCHS = {"LlamaForCausalLM": "llama", "MistralForCausalLM": "llama", "MixtralForCausalLM": "llama", "Qwen2ForCausalLM": "qwen2",
          "Qwen2MoeForCausalLM": "qwen2moe", "Qwen3ForCausalLM": "qwen3", "Qwen3MoeForCausalLM": "qwen3moe", "Phi3ForCausalLM": "phi3", "GraniteForCausalLM": "granite",
-         "SmolLM3ForCausalLM": "smollm3", "SeedOssForCausalLM": "seed_oss", "Ernie4_5ForCausalLM": "ernie4_5", "GraniteMoeForCausalLM": "granitemoe"}
+         "SmolLM3ForCausalLM": "smollm3", "SeedOssForCausalLM": "seed_oss", "Ernie4_5ForCausalLM": "ernie4_5", "GraniteMoeForCausalLM": "granitemoe",
+         "Starcoder2ForCausalLM": "starcoder2", "FalconForCausalLM": "falcon", "OlmoForCausalLM": "olmo", "CohereForCausalLM": "command-r"}
 # families whose GGUF graph rotates adjacent pairs: HF's half-split Q/K rows are permuted on the way in (ernie4_5 already stores
 # adjacent pairs upstream, so it is not in the list)
-PERMUTE_QK = ("llama", "granite", "granitemoe", "smollm3")
+PERMUTE_QK = ("llama", "granite", "granitemoe", "smollm3", "olmo")
+LAYERNORM = ("starcoder2", "falcon", "olmo", "command-r")
 LAYER_MAP = {
     "input_layernorm.weight": "attn_norm.weight", "post_attention_layernorm.weight": "ffn_norm.weight",
     "self_attn.q_proj.weight": "attn_q.weight", "self_attn.k_proj.weight": "attn_k.weight", "self_attn.v_proj.weight": "attn_v.weight",
@@ -36,8 +38,18 @@ LAYER_MAP = {
     "self_attn.k_norm.weight": "attn_k_norm.weight", "self_attn.qkv_proj.weight": "attn_qkv.weight",
     "mlp.gate_proj.weight": "ffn_gate.weight", "mlp.up_proj.weight": "ffn_up.weight", "mlp.down_proj.weight": "ffn_down.weight",
     "mlp.gate_up_proj.weight": "ffn_up.weight",
+    # LayerNorm families: norm and projection biases, starcoder2's non-gated MLP
+    "input_layernorm.bias": "attn_norm.bias", "post_attention_layernorm.bias": "ffn_norm.bias", "self_attn.o_proj.bias": "attn_output.bias",
+    "mlp.c_fc.weight": "ffn_up.weight", "mlp.c_fc.bias": "ffn_up.bias", "mlp.c_proj.weight": "ffn_down.weight", "mlp.c_proj.bias": "ffn_down.bias",
 }
-TOP_MAP = {"model.embed_tokens.weight": "token_embd.weight", "model.norm.weight": "output_norm.weight", "lm_head.weight": "output.weight"}
+# falcon keeps its own module names (transformer.h.N....); QKV is regrouped separately
+FALCON_MAP = {"input_layernorm.weight": "attn_norm.weight", "input_layernorm.bias": "attn_norm.bias",
+              "ln_mlp.weight": "attn_norm.weight", "ln_mlp.bias": "attn_norm.bias", "ln_attn.weight": "attn_norm_2.weight", "ln_attn.bias": "attn_norm_2.bias",
+              "self_attention.dense.weight": "attn_output.weight", "mlp.dense_h_to_4h.weight": "ffn_up.weight", "mlp.dense_4h_to_h.weight": "ffn_down.weight",
+              "self_attention.query_key_value.weight": "attn_qkv.weight"}
+TOP_MAP = {"model.embed_tokens.weight": "token_embd.weight", "model.norm.weight": "output_norm.weight", "lm_head.weight": "output.weight",
+           "model.norm.bias": "output_norm.bias", "transformer.word_embeddings.weight": "token_embd.weight",
+           "transformer.ln_f.weight": "output_norm.weight", "transformer.ln_f.bias": "output_norm.bias"}
 
 
 def permute_qk(w: np.ndarray, n_head: int) -> np.ndarray:
@@ -124,6 +136,8 @@ def convert(src: str, dst: str, outtype: str = "F16") -> str:
     E, L = cfg["hidden_size"], cfg["num_hidden_layers"]
     H = cfg["num_attention_heads"]
     Hkv = cfg.get("num_key_value_heads") or H
+    if a == "falcon":       # multi_query: one K/V head; new_decoder_architecture: num_kv_heads groups
+        Hkv = int(cfg.get("num_kv_heads") or H) if cfg.get("new_decoder_architecture") else (1 if cfg.get("multi_query", True) else H)
     D = cfg.get("head_dim") or E // H
     rope = cfg.get("rope_parameters") or {}
     theta = float(cfg.get("rope_theta") or rope.get("rope_theta") or 10000.0)
@@ -135,7 +149,7 @@ def convert(src: str, dst: str, outtype: str = "F16") -> str:
     w.add(f"{a}.context_length", cfg.get("max_position_embeddings", 2048), ValueType.UINT32)
     w.add(f"{a}.embedding_length", E, ValueType.UINT32)
     w.add(f"{a}.block_count", L, ValueType.UINT32)
-    w.add(f"{a}.feed_forward_length", cfg["intermediate_size"], ValueType.UINT32)
+    w.add(f"{a}.feed_forward_length", (cfg.get("ffn_hidden_size") or 4 * E) if a == "falcon" else cfg["intermediate_size"], ValueType.UINT32)
     if a in ("granite", "granitemoe"):
         w.add(f"{a}.embedding_scale", float(cfg.get("embedding_multiplier", 1.0)), ValueType.FLOAT32)
         w.add(f"{a}.residual_scale", float(cfg.get("residual_multiplier", 1.0)), ValueType.FLOAT32)
@@ -151,7 +165,14 @@ def convert(src: str, dst: str, outtype: str = "F16") -> str:
             w.add(f"{a}.expert_shared_feed_forward_length", int(cfg["shared_expert_intermediate_size"]), ValueType.UINT32)
     w.add(f"{a}.attention.head_count", H, ValueType.UINT32)
     w.add(f"{a}.attention.head_count_kv", Hkv, ValueType.UINT32)
-    w.add(f"{a}.attention.layer_norm_rms_epsilon", float(cfg.get("rms_norm_eps", 1e-5)), ValueType.FLOAT32)
+    if a in LAYERNORM:
+        w.add(f"{a}.attention.layer_norm_epsilon", float(cfg.get("norm_epsilon") or cfg.get("layer_norm_epsilon") or cfg.get("layer_norm_eps") or 1e-5), ValueType.FLOAT32)
+        if a == "command-r":
+            w.add(f"{a}.logit_scale", float(cfg.get("logit_scale", 1.0)), ValueType.FLOAT32)
+        if a == "olmo" and cfg.get("clip_qkv"):
+            raise SystemExit("olmo checkpoints with clip_qkv are not supported (the fused RoPE / cache-write kernel does not clamp)")
+    else:
+        w.add(f"{a}.attention.layer_norm_rms_epsilon", float(cfg.get("rms_norm_eps", 1e-5)), ValueType.FLOAT32)
     w.add(f"{a}.rope.freq_base", theta, ValueType.FLOAT32)
     w.add(f"{a}.rope.dimension_count", D, ValueType.UINT32)
     if D * H != E:
@@ -232,6 +253,11 @@ def convert(src: str, dst: str, outtype: str = "F16") -> str:
             out = name[len("__moe__."):]
         elif name in TOP_MAP:
             out = TOP_MAP[name]
+        elif a == "falcon":
+            m = re.match(r"transformer\.h\.(\d+)\.(.+)", name)
+            if not m or m.group(2) not in FALCON_MAP:
+                raise SystemExit(f"unmapped tensor {name}")
+            out = f"blk.{m.group(1)}.{FALCON_MAP[m.group(2)]}"
         else:
             m = re.match(r"model\.layers\.(\d+)\.(.+)", name)
             if not m or m.group(2) not in LAYER_MAP:
@@ -240,6 +266,10 @@ def convert(src: str, dst: str, outtype: str = "F16") -> str:
         if name == "lm_head.weight" and cfg.get("tie_word_embeddings"):
             continue
         t = tensors[name].float().numpy()
+        if a == "falcon" and out.endswith("attn_qkv.weight"):
+            # HF groups the rows per K/V head as [that group's query heads..., its key head, its value head]; GGUF wants [all Q | all K | all V]
+            g = t.reshape(Hkv, H // Hkv + 2, D, E)
+            t = np.concatenate([g[:, :-2].reshape(H * D, E), g[:, -2].reshape(Hkv * D, E), g[:, -1].reshape(Hkv * D, E)], 0)
         if a == "seed_oss" and out.endswith("ffn_norm.weight"):
             out = out.replace("ffn_norm.weight", "post_attention_norm.weight")
         if a in PERMUTE_QK and out.endswith("attn_q.weight"):
