@@ -119,6 +119,8 @@ def norm_layout(cfg: ModelConfig) -> dict:
     if cfg.norm_type != "layer":
         return {"attn": "w", "ffn": "w", "out": "w"}
     return {"starcoder2": {"attn": "wb", "ffn": "wb", "out": "wb"}, "orion": {"attn": "wb", "ffn": "wb", "out": "wb"},
+            "gptneox": {"attn": "wb", "ffn": "wb", "out": "wb"}, "stablelm": {"attn": "wb", "ffn": "wb", "out": "wb"},
+            "nemotron": {"attn": "wb", "ffn": "wb", "out": "wb"},
             "falcon": {"attn": "wb", "ffn": "", "out": "wb"}, "command-r": {"attn": "w", "ffn": "", "out": "w"},
             "olmo": {"attn": "", "ffn": "", "out": ""}}.get(cfg.arch, {"attn": "wb", "ffn": "" if cfg.parallel_residual else "wb", "out": "wb"})
 
@@ -127,7 +129,7 @@ def _tensor_plan(cfg: ModelConfig, rope_freqs: bool):
     """(name, shape, layer, init_std) for every tensor of the architecture; shapes row-major [out, in]."""
     E, F = cfg.n_embd, cfg.n_ff
     nl = norm_layout(cfg)
-    all_bias = cfg.arch == "starcoder2"       # biases on the attention output and the MLP as well
+    all_bias = cfg.arch in ("starcoder2", "gptneox")       # biases on the attention output and the MLP as well
 
     def norm(name, il, kind):
         return ([(name + ".weight", (E,), il, 0.0)] if "w" in kind else []) + ([(name + ".bias", (E,), il, 0.05)] if "b" in kind else [])
@@ -139,11 +141,13 @@ def _tensor_plan(cfg: ModelConfig, rope_freqs: bool):
         plan += norm(p + "attn_norm", il, nl["attn"])
         if cfg.fused_qkv:
             plan.append((p + "attn_qkv.weight", (cfg.q_dim + 2 * cfg.kv_dim, E), il, 0.02))
+            if cfg.qkv_bias:
+                plan.append((p + "attn_qkv.bias", (cfg.q_dim + 2 * cfg.kv_dim,), il, 0.05))
         else:
             plan += [(p + "attn_q.weight", (cfg.q_dim, E), il, 0.02),
                      (p + "attn_k.weight", (cfg.kv_dim, E), il, 0.02),
                      (p + "attn_v.weight", (cfg.kv_dim, E), il, 0.02)]
-        if cfg.qkv_bias:
+        if cfg.qkv_bias and not cfg.fused_qkv:
             plan += [(p + "attn_q.bias", (cfg.q_dim,), il, 0.05), (p + "attn_k.bias", (cfg.kv_dim,), il, 0.05),
                      (p + "attn_v.bias", (cfg.kv_dim,), il, 0.05)]
         if cfg.qk_norm:
@@ -155,7 +159,7 @@ def _tensor_plan(cfg: ModelConfig, rope_freqs: bool):
             plan += norm(p + "ffn_norm", il, nl["ffn"])
         else:
             plan.append((p + cfg.ffn_norm_name, (E,), il, 0.0))
-        if cfg.ffn_act == "gelu":       # non-gated MLP
+        if cfg.ffn_act in ("gelu", "relu2"):       # non-gated MLP
             plan += [(p + "ffn_up.weight", (F, E), il, 0.02), (p + "ffn_down.weight", (E, F), il, 0.02)]
             if all_bias:
                 plan += [(p + "ffn_up.bias", (F,), il, 0.05), (p + "ffn_down.bias", (E,), il, 0.05)]
@@ -225,6 +229,8 @@ def write_synthetic_gguf(path: str, cfg: ModelConfig, ftype: str = "F16", seed: 
     elif cfg.rope_scale_linear != 1.0:
         w.add(f"{a}.rope.scaling.type", "linear")
         w.add(f"{a}.rope.scaling.factor", float(1.0 / cfg.rope_scale_linear), ValueType.FLOAT32)
+    if a == "gptneox":
+        w.add(f"{a}.use_parallel_residual", bool(cfg.parallel_residual))
     if cfg.is_moe:
         if a != "llama":
             w.add(f"{a}.expert_feed_forward_length", cfg.n_ff, ValueType.UINT32)

@@ -53,7 +53,7 @@ class ModelConfig:
     n_ff_shared: int = 0           # > 0: shared-expert FFN width (`ffn_*_shexp`, gate vector `ffn_gate_inp_shexp`)
     # LayerNorm / GELU / parallel-residual families (starcoder2, falcon, olmo, orion, command-r): the generic layer path
     norm_type: str = "rms"         # "rms" | "layer" (mean-centred; weight and bias optional per file: olmo has neither)
-    ffn_act: str = "swiglu"        # "swiglu" (gated SiLU) | "gelu" (ffn_up -> GELU -> ffn_down, biases optional)
+    ffn_act: str = "swiglu"        # "swiglu" (gated SiLU) | "gelu" | "relu2" (non-gated: ffn_up -> activation -> ffn_down, biases optional)
     parallel_residual: bool = False  # h + attn(n(h)) + ffn(n'(h)) instead of the sequential form (falcon, command-r)
     fused_gate_up: bool = False    # phi3: ffn_up holds [gate | up]
 
@@ -168,6 +168,15 @@ PRESETS: dict[str, ModelConfig] = {
                              head_dim=64, n_ff=512, n_ctx_train=512, rope_theta=10000.0, rope_dim=64, norm_type="layer"),
     "tiny-orion": ModelConfig(name="tiny-orion", arch="orion", vocab_size=512, n_embd=256, n_layer=2, n_head=4, n_head_kv=4,
                               head_dim=64, n_ff=512, n_ctx_train=512, rope_theta=10000.0, rope_dim=64, rope_neox=True, norm_type="layer"),
+    "tiny-gptneox": ModelConfig(name="tiny-gptneox", arch="gptneox", vocab_size=512, n_embd=256, n_layer=2, n_head=4, n_head_kv=4,
+                                head_dim=64, n_ff=1024, n_ctx_train=512, rope_theta=10000.0, rope_dim=16, rope_neox=True, fused_qkv=True, qkv_bias=True,
+                                norm_type="layer", ffn_act="gelu", parallel_residual=True),
+    "tiny-stablelm": ModelConfig(name="tiny-stablelm", arch="stablelm", vocab_size=512, n_embd=256, n_layer=2, n_head=4, n_head_kv=2,
+                                 head_dim=64, n_ff=512, n_ctx_train=512, rope_theta=10000.0, rope_dim=32, rope_neox=True, norm_type="layer"),
+    "tiny-nemotron": ModelConfig(name="tiny-nemotron", arch="nemotron", vocab_size=512, n_embd=256, n_layer=2, n_head=4, n_head_kv=2,
+                                 head_dim=64, n_ff=1024, n_ctx_train=512, rope_theta=10000.0, rope_dim=32, rope_neox=True, norm_type="layer", ffn_act="relu2"),
+    "tiny-arcee": ModelConfig(name="tiny-arcee", arch="arcee", vocab_size=512, n_embd=256, n_layer=2, n_head=4, n_head_kv=2,
+                              head_dim=64, n_ff=1024, n_ctx_train=512, rope_theta=10000.0, rope_dim=64, ffn_act="relu2"),
     "tiny-command-r": ModelConfig(name="tiny-command-r", arch="command-r", vocab_size=512, n_embd=256, n_layer=2, n_head=4, n_head_kv=2,
                                   head_dim=64, n_ff=512, n_ctx_train=512, rope_theta=10000.0, rope_dim=64, norm_type="layer",
                                   parallel_residual=True, logit_scale=16.0, tie_embeddings=True),
@@ -206,12 +215,15 @@ PRESETS: dict[str, ModelConfig] = {
 #   minicpm, granitemoe - the granite builder (four scalars; granitemoe with routed experts);   smollm3 - no rotation on every 4th layer.
 SUPPORTED_ARCHS = {"llama", "qwen2", "qwen2moe", "qwen3", "qwen3moe", "phi3", "granite",
                    "internlm2", "xverse", "ernie4_5", "exaone", "seed_oss", "minicpm", "granitemoe", "smollm3",
-                   "starcoder2", "falcon", "olmo", "orion", "command-r"}
-ROPE_NORM_ARCHS = {"llama", "granite", "granitemoe", "minicpm", "internlm2", "xverse", "ernie4_5", "smollm3", "olmo", "command-r"}     # llama_model_rope_type
+                   "starcoder2", "falcon", "olmo", "orion", "command-r", "gptneox", "stablelm", "nemotron", "arcee"}
+ROPE_NORM_ARCHS = {"llama", "granite", "granitemoe", "minicpm", "internlm2", "xverse", "ernie4_5", "smollm3", "olmo", "command-r", "arcee"}     # llama_model_rope_type
 # LayerNorm families and what differs beyond the norm (llama.cpp/src/models/{starcoder2,falcon,olmo,orion,command-r}.cpp):
 #   starcoder2: biases on every matrix, non-gated GELU MLP;  falcon: fused QKV, GELU MLP, attention and MLP in parallel from the same
 #   (or a second) norm;  olmo: norms without parameters;  orion: llama with LayerNorm;  command-r: parallel, logits * logit_scale
-LAYERNORM_ARCHS = {"starcoder2", "falcon", "olmo", "orion", "command-r"}
+#   gptneox (pythia): fused QKV with bias, rotary on part of each head, GELU MLP with biases, parallel blocks with a second norm for the MLP
+#   stablelm: rotary on part of each head, gated SiLU MLP
+#   nemotron: rotary on part of each head, non-gated ReLU^2 MLP;   arcee keeps RMSNorm but has the same non-gated ReLU^2 MLP
+LAYERNORM_ARCHS = {"starcoder2", "falcon", "olmo", "orion", "command-r", "gptneox", "stablelm", "nemotron"}
 
 
 def preset(name: str, **overrides) -> ModelConfig:
@@ -265,14 +277,15 @@ def config_from_gguf(meta: dict[str, Any], tensors: dict | None = None) -> Model
         n_ff=int(g("expert_feed_forward_length") or g("feed_forward_length")) if int(g("expert_count", 0) or 0) > 0 else int(g("feed_forward_length")),
         n_ctx_train=int(g("context_length", 2048)),
         rms_eps=float(g("attention.layer_norm_epsilon", 1e-5) if arch in LAYERNORM_ARCHS else g("attention.layer_norm_rms_epsilon", 1e-5)),
-        norm_type="layer" if arch in LAYERNORM_ARCHS else "rms", ffn_act="gelu" if arch in ("starcoder2", "falcon") else "swiglu",
-        parallel_residual=arch in ("falcon", "command-r"), fused_gate_up=arch == "phi3", rope_theta=float(g("rope.freq_base", 10000.0)),
+        norm_type="layer" if arch in LAYERNORM_ARCHS else "rms", ffn_act="gelu" if arch in ("starcoder2", "falcon", "gptneox") else "relu2" if arch in ("nemotron", "arcee") else "swiglu",
+        parallel_residual=arch in ("falcon", "command-r") or (arch == "gptneox" and bool(g("use_parallel_residual", True)))
+        or (arch == "stablelm" and tensors is not None and "blk.0.ffn_norm.weight" not in tensors), fused_gate_up=arch == "phi3", rope_theta=float(g("rope.freq_base", 10000.0)),
         rope_dim=int(g("rope.dimension_count", head_dim)), rope_neox=arch not in ROPE_NORM_ARCHS, rope_scale_linear=scale,
         embedding_scale=float(g("embedding_scale") or dflt["embedding_scale"]), residual_scale=float(g("residual_scale") or dflt["residual_scale"]),
         logit_scale=(1.0 / float(g("logit_scale") or 1.0)) if arch == "command-r" else float(g("logit_scale") or dflt["logit_scale"]), attention_scale=float(g("attention.scale", 0.0) or 0.0),
         no_rope_step=4 if arch == "smollm3" else 0,
         moe_norm_topk=arch != "qwen2moe", n_ff_shared=int(g("expert_shared_feed_forward_length", 0) or 0),
-        qkv_bias=arch in ("qwen2", "qwen2moe") or (tensors is not None and "blk.0.attn_q.bias" in tensors),
+        qkv_bias=arch in ("qwen2", "qwen2moe") or (tensors is not None and ("blk.0.attn_q.bias" in tensors or "blk.0.attn_qkv.bias" in tensors)),
         qk_norm=arch in ("qwen3", "qwen3moe") or (tensors is not None and "blk.0.attn_q_norm.weight" in tensors),
         fused_qkv=arch == "phi3" or (tensors is not None and "blk.0.attn_qkv.weight" in tensors),
         n_expert=int(g("expert_count", 0) or 0), n_expert_used=int(g("expert_used_count", 0) or 0),

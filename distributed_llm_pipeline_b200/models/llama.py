@@ -106,6 +106,8 @@ class LlamaEngine:
             n_pages = max_pages * max_seqs
         self.kv = PagedKVCache(cfg, weights.layer_range, self.Hkv, n_pages, page_size, max_seqs, max_pages, dev)
         self.inv_freq = rope_inv_freq(cfg, weights.rope_freqs.cpu() if weights.rope_freqs is not None else None).to(dev)
+        if cfg.rope_dim < cfg.head_dim:     # partial rotary: zero angles for the dims left alone (Wq / Wk rows were re-ordered at load, models/weights.py)
+            self.inv_freq = torch.cat([self.inv_freq, torch.zeros(cfg.head_dim // 2 - cfg.rope_dim // 2, dtype=self.inv_freq.dtype, device=dev)])
         # layers without rotary encoding (smollm3: every 4th) run the same kernels on a zero-angle table: the rotation is the identity
         self.inv_freq_off = torch.zeros_like(self.inv_freq) if cfg.no_rope_step > 0 else None
         self.attn_scale = rope_attn_scale(cfg)
@@ -143,7 +145,8 @@ class LlamaEngine:
         self.act = torch.zeros(M, self.F, dtype=f16, device=dev)
         # generic layer path: fp32 MLP pre-activation (bias + GELU run between the two mat-muls), second norm output (falcon-40b)
         self.up32 = torch.zeros(M, self.F, dtype=f32, device=dev) if cfg.ffn_act != "swiglu" else None
-        self.xn2 = torch.zeros(M, self.E, dtype=f16, device=dev) if any(lw.attn_norm2 is not None for lw in weights.layers.values()) else None
+        self.xn2 = torch.zeros(M, self.E, dtype=f16, device=dev) if any(lw.attn_norm2 is not None or (cfg.parallel_residual and lw.ffn_norm is not None)
+                                                                         for lw in weights.layers.values()) else None
         self.tokens = torch.zeros(M, dtype=i32, device=dev)
         self.pos = torch.zeros(M, dtype=i32, device=dev)
         self.slot = torch.zeros(M, dtype=i32, device=dev)
@@ -360,7 +363,11 @@ class LlamaEngine:
         h = self.h[:T]
         tp = comm.tp_size > 1
         xn = self._norm(h, lw.attn_norm, lw.attn_norm_b, out=self.xn[:T])
-        xa = self._norm(h, lw.attn_norm2, lw.attn_norm2_b, out=self.xn2[:T]) if lw.attn_norm2 is not None else xn
+        xa, xf = xn, xn
+        if lw.attn_norm2 is not None:                         # falcon-40b: the attention branch has its own norm of the block input
+            xa = self._norm(h, lw.attn_norm2, lw.attn_norm2_b, out=self.xn2[:T])
+        elif cfg.parallel_residual and lw.ffn_norm is not None:   # gptneox: the MLP branch has its own norm of the block input
+            xf = self._norm(h, lw.ffn_norm, lw.ffn_norm_b, out=self.xn2[:T])
         qkv = self.qkv16[:T]
         if lw.wv is None:
             ops.linear(lw.wqkv, xa, "f16", out=qkv, scratch=self._scratch_for(lw.wqkv))
@@ -376,12 +383,12 @@ class LlamaEngine:
             d.add_(lw.bo)
         if cfg.parallel_residual:       # the MLP reads the norm of the block INPUT: add the attention branch to h only now
             h.add_(d)
-            ffn_in = xn
+            ffn_in = xf
         else:
             ffn_in = self._norm(h, lw.ffn_norm, lw.ffn_norm_b, delta=d, out=self.xn[:T])       # h += d inside
-        if cfg.ffn_act == "gelu":
+        if cfg.ffn_act in ("gelu", "relu2"):
             up = ops.linear(lw.w_up, ffn_in, "f32", out=self.up32[:T], scratch=self._scratch_for(lw.w_up))
-            act = ops.bias_act(up, lw.b_up, "gelu", out=self.act[:T])
+            act = ops.bias_act(up, lw.b_up, cfg.ffn_act, out=self.act[:T])
         else:
             act = ops.linear(lw.w_gate, ffn_in, "swiglu", w_up=lw.w_up, out=self.act[:T], scratch=self._scratch_for(lw.w_gate, lw.w_up))
         d = ops.linear(lw.w_down, act, "f32", out=self.delta[:T], scratch=self._scratch_for(lw.w_down))

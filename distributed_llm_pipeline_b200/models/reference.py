@@ -134,10 +134,13 @@ class ReferenceModel:
         p = f"blk.{il}."
         T = x.shape[0]
         if c.fused_qkv:   # phi3: one [q | k | v] matrix (llama.cpp/src/models/phi3.cpp)
-            q, k, v = self.mm(x, p + "attn_qkv.weight").split([c.q_dim, c.kv_dim, c.kv_dim], dim=-1)
+            qkv = self.mm(x, p + "attn_qkv.weight")
+            if p + "attn_qkv.bias" in w:      # gptneox
+                qkv = qkv + w[p + "attn_qkv.bias"]
+            q, k, v = qkv.split([c.q_dim, c.kv_dim, c.kv_dim], dim=-1)
         else:
             q, k, v = (self.mm(x, p + f"attn_{n}.weight") for n in "qkv")
-        if c.qkv_bias:    # qwen2 (llama.cpp/src/models/qwen2.cpp)
+        if c.qkv_bias and not c.fused_qkv:    # qwen2 (llama.cpp/src/models/qwen2.cpp)
             q, k, v = (t + w[p + f"attn_{n}.bias"] for t, n in zip((q, k, v), "qkv"))
         q = q.reshape(T, c.n_head, c.head_dim)
         k = k.reshape(T, c.n_head_kv, c.head_dim)
@@ -166,11 +169,12 @@ class ReferenceModel:
     def ffn(self, il: int, x: torch.Tensor) -> torch.Tensor:
         c, w = self.cfg, self.w
         p = f"blk.{il}."
-        if c.ffn_act == "gelu":   # non-gated MLP with optional biases (starcoder2, falcon); GELU in its tanh form, as ggml computes it
+        if c.ffn_act in ("gelu", "relu2"):   # non-gated MLP with optional biases; GELU in its tanh form, as ggml computes it
             up = self.mm(x, p + "ffn_up.weight")
             if p + "ffn_up.bias" in w:
                 up = up + w[p + "ffn_up.bias"]
-            dn = self.mm(torch.nn.functional.gelu(up, approximate="tanh"), p + "ffn_down.weight")
+            a = torch.nn.functional.gelu(up, approximate="tanh") if c.ffn_act == "gelu" else torch.relu(up) ** 2
+            dn = self.mm(a, p + "ffn_down.weight")
             return dn + w[p + "ffn_down.bias"] if p + "ffn_down.bias" in w else dn
         if c.fused_gate_up:   # phi3: ffn_up holds [gate | up]; swiglu = silu(first half) * second half
             g, u = self.mm(x, p + "ffn_up.weight").split([c.n_ff, c.n_ff], dim=-1)
@@ -208,6 +212,8 @@ class ReferenceModel:
         p = f"blk.{il}."
         if c.parallel_residual:     # falcon, command-r: both branches read the block input (falcon-40b: through two different norms)
             xn = self.norm(h, p + "attn_norm")
+            if p + "ffn_norm.weight" in w:      # gptneox: attention reads attn_norm(h), the MLP ffn_norm(h)
+                return h + self.attention(il, xn, pos, cache) + self.ffn(il, self.norm(h, p + "ffn_norm"))
             xa = self.norm(h, p + "attn_norm_2") if p + "attn_norm_2.weight" in w else xn
             return h + self.attention(il, xa, pos, cache) + self.ffn(il, xn)
         h = h + c.residual_scale * self.attention(il, self.norm(h, p + "attn_norm"), pos, cache)

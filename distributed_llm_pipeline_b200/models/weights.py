@@ -155,7 +155,8 @@ def load_weights(src: str | GGUFModelFiles, device, layer_range: range | None = 
     def f32(name):
         return torch.from_numpy(np.array(f.array(name), dtype=np.float32, copy=True)).to(dev)
 
-    def mat(name, rows=None, cols=None, sub=None, scale: float = 1.0) -> DeviceWeight:
+    def mat(name, rows=None, cols=None, sub=None, scale: float = 1.0, perm=None) -> DeviceWeight:
+        """`perm`: gather of the (sliced) output rows - the partial-rotary head re-ordering below."""
         t = f.tensors[name]
         raw = f.raw(name)
         shape = t.shape
@@ -183,9 +184,26 @@ def load_weights(src: str | GGUFModelFiles, device, layer_range: range | None = 
                 dense = dense[rows[0]:rows[1]]
             if cols is not None:
                 dense = dense[:, cols[0]:cols[1]]
+            if perm is not None:
+                dense = dense[perm]
             dense = np.ascontiguousarray(dense)
             return DeviceWeight.from_raw(quantize(dense, GGMLType.F16), GGMLType.F16, dense.shape, dev)
+        if perm is not None:
+            raw2 = np.ascontiguousarray(raw2.reshape(shp[0], -1)[perm])
         return DeviceWeight.from_raw(raw2, ttype, shp, dev)
+
+    # Rotary on only the first n_rot dims of each head with half-split pairs (i, i + n_rot/2) - gptneox, stablelm: the kernels rotate
+    # pairs (j, j + D/2) over the whole head.  Re-ordering the rows of Wq / Wk inside every head so that the rotated dims land on
+    # [0, n_rot/2) and [D/2, D/2 + n_rot/2) - the rest gets a zero angle - gives the same scores, since Q.K is invariant under one
+    # permutation applied to both.  V and everything downstream are untouched.
+    def head_perm(n_heads: int):
+        r = cfg.rope_dim // 2
+        if cfg.rope_dim >= D or not cfg.rope_neox:
+            return None
+        one = list(range(r)) + list(range(cfg.rope_dim, cfg.rope_dim + D // 2 - r)) + list(range(r, cfg.rope_dim)) + \
+            list(range(cfg.rope_dim + D // 2 - r, D))
+        return np.concatenate([np.asarray(one) + h * D for h in range(n_heads)])
+    perm_q, perm_k = head_perm(hq1 - hq0), head_perm(n_kv_local)
 
     layers: dict[int, LayerWeights] = {}
     for il in layer_range:
@@ -194,12 +212,12 @@ def load_weights(src: str | GGUFModelFiles, device, layer_range: range | None = 
         kr = (kv_rank * n_kv_local * D, (kv_rank + 1) * n_kv_local * D)
         if cfg.fused_qkv:   # phi3: rows [q | k | v] of one tensor
             ko, vo = cfg.q_dim, cfg.q_dim + cfg.kv_dim
-            wq = mat(p + "attn_qkv.weight", rows=qr)
-            wk = mat(p + "attn_qkv.weight", rows=(ko + kr[0], ko + kr[1]))
+            wq = mat(p + "attn_qkv.weight", rows=qr, perm=perm_q)
+            wk = mat(p + "attn_qkv.weight", rows=(ko + kr[0], ko + kr[1]), perm=perm_k)
             wv = mat(p + "attn_qkv.weight", rows=(vo + kr[0], vo + kr[1]))
         else:
-            wq = mat(p + "attn_q.weight", rows=qr)
-            wk = mat(p + "attn_k.weight", rows=kr)
+            wq = mat(p + "attn_q.weight", rows=qr, perm=perm_q)
+            wk = mat(p + "attn_k.weight", rows=kr, perm=perm_k)
             wv = mat(p + "attn_v.weight", rows=kr)
         wv_sep = None
         if wq.wtype == wk.wtype == wv.wtype:
@@ -230,12 +248,18 @@ def load_weights(src: str | GGUFModelFiles, device, layer_range: range | None = 
             lw.attn_norm2, lw.attn_norm2_b = opt(p + "attn_norm_2.weight"), opt(p + "attn_norm_2.bias")
             lw.bo, lw.b_down = opt(p + "attn_output.bias"), opt(p + "ffn_down.bias")
         if cfg.qkv_bias:
-            lw.qkv_bias = torch.cat([f32(p + "attn_q.bias")[qr[0]:qr[1]], f32(p + "attn_k.bias")[kr[0]:kr[1]],
-                                     f32(p + "attn_v.bias")[kr[0]:kr[1]]]).contiguous()
+            if cfg.fused_qkv:       # gptneox: one bias vector laid out like the fused matrix
+                fb = f32(p + "attn_qkv.bias")
+                bq, bk, bv = fb[qr[0]:qr[1]], fb[cfg.q_dim + kr[0]:cfg.q_dim + kr[1]], fb[cfg.q_dim + cfg.kv_dim + kr[0]:cfg.q_dim + cfg.kv_dim + kr[1]]
+            else:
+                bq, bk, bv = f32(p + "attn_q.bias")[qr[0]:qr[1]], f32(p + "attn_k.bias")[kr[0]:kr[1]], f32(p + "attn_v.bias")[kr[0]:kr[1]]
+            if perm_q is not None:
+                bq, bk = bq[torch.as_tensor(perm_q, device=bq.device)], bk[torch.as_tensor(perm_k, device=bk.device)]
+            lw.qkv_bias = torch.cat([bq, bk, bv]).contiguous()
         if cfg.qk_norm:
             lw.q_norm, lw.k_norm = f32(p + "attn_q_norm.weight"), f32(p + "attn_k_norm.weight")
         f0, f1 = _split(cfg.n_ff, tp_size, tp_rank, 256 if tp_size > 1 else 1)
-        if cfg.ffn_act == "gelu":     # non-gated MLP: up -> GELU -> down
+        if cfg.ffn_act in ("gelu", "relu2"):     # non-gated MLP: up -> activation -> down
             lw.w_up = mat(p + "ffn_up.weight", rows=(f0, f1))
             lw.w_down = mat(p + "ffn_down.weight", cols=(f0, f1), scale=cfg.residual_scale)
             if p + "ffn_up.bias" in f:

@@ -46,6 +46,14 @@ CASES = {
                                                      "num_kv_heads": None, "activation": "gelu_pytorch_tanh", "tie_word_embeddings": False, "ffn_hidden_size": 1024}),
     "falcon-new-arch": ("FalconConfig", "FalconForCausalLM", {"multi_query": False, "new_decoder_architecture": True, "parallel_attn": True, "bias": False, "alibi": False,
                                                               "num_kv_heads": 2, "activation": "gelu_pytorch_tanh", "tie_word_embeddings": False, "ffn_hidden_size": 1024}),
+    "gptneox": ("GPTNeoXConfig", "GPTNeoXForCausalLM", {"rotary_pct": 0.25, "use_parallel_residual": True, "hidden_act": "gelu_pytorch_tanh", "layer_norm_eps": 1e-5,
+                                                      "attention_bias": True, "intermediate_size": 1024}),
+    "gptneox-seq": ("GPTNeoXConfig", "GPTNeoXForCausalLM", {"rotary_pct": 0.5, "use_parallel_residual": False, "hidden_act": "gelu_pytorch_tanh", "layer_norm_eps": 1e-5,
+                                                          "attention_bias": True, "intermediate_size": 1024}),
+    "stablelm": ("StableLmConfig", "StableLmForCausalLM", {"partial_rotary_factor": 0.25, "layer_norm_eps": 1e-5, "use_qkv_bias": False}),
+    "nemotron": ("NemotronConfig", "NemotronForCausalLM", {"partial_rotary_factor": 0.5, "norm_eps": 1e-5, "hidden_act": "relu2", "intermediate_size": 1024,
+                                                         "attention_bias": False, "mlp_bias": False, "head_dim": 64}),
+    "arcee": ("ArceeConfig", "ArceeForCausalLM", {"hidden_act": "relu2", "intermediate_size": 1024, "head_dim": 64, "attention_bias": False, "mlp_bias": False}),
     "olmo": ("OlmoConfig", "OlmoForCausalLM", {"clip_qkv": None, "num_key_value_heads": 4}),
     "command-r": ("CohereConfig", "CohereForCausalLM", {"logit_scale": 0.0625, "layer_norm_eps": 1e-5, "use_qk_norm": False, "tie_word_embeddings": True}),
     "qwen3moe": ("Qwen3MoeConfig", "Qwen3MoeForCausalLM", {"head_dim": 64, "moe_intermediate_size": 128, "num_experts": 4,

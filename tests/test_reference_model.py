@@ -67,7 +67,10 @@ def test_rope_modes():
                                  ("tiny-seed-oss", "F16"), ("tiny-minicpm", "F16"), ("tiny-granitemoe", "F16"), ("tiny-smollm3", "F16"), ("tiny-smollm3", "Q8_0"),
                                  # LayerNorm / GELU / parallel-residual families: the generic layer path
                                  ("tiny-starcoder2", "F16"), ("tiny-starcoder2", "Q8_0"), ("tiny-falcon", "F16"), ("tiny-falcon", "Q8_0"), ("tiny-olmo", "F16"),
-                                 ("tiny-orion", "F16"), ("tiny-command-r", "F16")])
+                                 ("tiny-orion", "F16"), ("tiny-command-r", "F16"),
+                                 # rotary on part of each head (the engine re-orders Wq / Wk rows and pads the angle table)
+                                 ("tiny-gptneox", "F16"), ("tiny-gptneox", "Q8_0"), ("tiny-stablelm", "F16"),
+                                 ("tiny-nemotron", "F16"), ("tiny-arcee", "F16")])        # non-gated ReLU^2 MLP
 def test_other_architectures_match_oracle_cpu(tmp_models, key):
     """qwen2 (QKV bias), qwen3 (per-head Q/K norm) and phi3 (fused QKV / gate-up tensors), all with half-split RoPE:
     engine (CPU op fallbacks, paged KV) against the fp32 oracle."""

@@ -25,11 +25,12 @@ from distributed_llm_pipeline_b200.gguf.synth import synthetic_vocab  # noqa: E4
 ARCHS = {"LlamaForCausalLM": "llama", "MistralForCausalLM": "llama", "MixtralForCausalLM": "llama", "Qwen2ForCausalLM": "qwen2",
          "Qwen2MoeForCausalLM": "qwen2moe", "Qwen3ForCausalLM": "qwen3", "Qwen3MoeForCausalLM": "qwen3moe", "Phi3ForCausalLM": "phi3", "GraniteForCausalLM": "granite",
          "SmolLM3ForCausalLM": "smollm3", "SeedOssForCausalLM": "seed_oss", "Ernie4_5ForCausalLM": "ernie4_5", "GraniteMoeForCausalLM": "granitemoe",
-         "Starcoder2ForCausalLM": "starcoder2", "FalconForCausalLM": "falcon", "OlmoForCausalLM": "olmo", "CohereForCausalLM": "command-r"}
+         "Starcoder2ForCausalLM": "starcoder2", "FalconForCausalLM": "falcon", "OlmoForCausalLM": "olmo", "CohereForCausalLM": "command-r",
+         "GPTNeoXForCausalLM": "gptneox", "StableLmForCausalLM": "stablelm", "NemotronForCausalLM": "nemotron", "ArceeForCausalLM": "arcee"}
 # families whose GGUF graph rotates adjacent pairs: HF's half-split Q/K rows are permuted on the way in (ernie4_5 already stores
 # adjacent pairs upstream, so it is not in the list)
-PERMUTE_QK = ("llama", "granite", "granitemoe", "smollm3", "olmo")
-LAYERNORM = ("starcoder2", "falcon", "olmo", "command-r")
+PERMUTE_QK = ("llama", "granite", "granitemoe", "smollm3", "olmo", "arcee")
+LAYERNORM = ("starcoder2", "falcon", "olmo", "command-r", "gptneox", "stablelm", "nemotron")
 LAYER_MAP = {
     "input_layernorm.weight": "attn_norm.weight", "post_attention_layernorm.weight": "ffn_norm.weight",
     "self_attn.q_proj.weight": "attn_q.weight", "self_attn.k_proj.weight": "attn_k.weight", "self_attn.v_proj.weight": "attn_v.weight",
@@ -47,9 +48,15 @@ FALCON_MAP = {"input_layernorm.weight": "attn_norm.weight", "input_layernorm.bia
               "ln_mlp.weight": "attn_norm.weight", "ln_mlp.bias": "attn_norm.bias", "ln_attn.weight": "attn_norm_2.weight", "ln_attn.bias": "attn_norm_2.bias",
               "self_attention.dense.weight": "attn_output.weight", "mlp.dense_h_to_4h.weight": "ffn_up.weight", "mlp.dense_4h_to_h.weight": "ffn_down.weight",
               "self_attention.query_key_value.weight": "attn_qkv.weight"}
+NEOX_MAP = {"input_layernorm.weight": "attn_norm.weight", "input_layernorm.bias": "attn_norm.bias", "post_attention_layernorm.weight": "ffn_norm.weight",
+            "post_attention_layernorm.bias": "ffn_norm.bias", "attention.query_key_value.weight": "attn_qkv.weight", "attention.query_key_value.bias": "attn_qkv.bias",
+            "attention.dense.weight": "attn_output.weight", "attention.dense.bias": "attn_output.bias", "mlp.dense_h_to_4h.weight": "ffn_up.weight",
+            "mlp.dense_h_to_4h.bias": "ffn_up.bias", "mlp.dense_4h_to_h.weight": "ffn_down.weight", "mlp.dense_4h_to_h.bias": "ffn_down.bias"}
 TOP_MAP = {"model.embed_tokens.weight": "token_embd.weight", "model.norm.weight": "output_norm.weight", "lm_head.weight": "output.weight",
            "model.norm.bias": "output_norm.bias", "transformer.word_embeddings.weight": "token_embd.weight",
-           "transformer.ln_f.weight": "output_norm.weight", "transformer.ln_f.bias": "output_norm.bias"}
+           "transformer.ln_f.weight": "output_norm.weight", "transformer.ln_f.bias": "output_norm.bias",
+           "gpt_neox.embed_in.weight": "token_embd.weight", "gpt_neox.final_layer_norm.weight": "output_norm.weight",
+           "gpt_neox.final_layer_norm.bias": "output_norm.bias", "embed_out.weight": "output.weight"}
 
 
 def permute_qk(w: np.ndarray, n_head: int) -> np.ndarray:
@@ -136,6 +143,8 @@ def convert(src: str, dst: str, outtype: str = "F16") -> str:
     E, L = cfg["hidden_size"], cfg["num_hidden_layers"]
     H = cfg["num_attention_heads"]
     Hkv = cfg.get("num_key_value_heads") or H
+    if a == "gptneox":      # always multi-head
+        Hkv = H
     if a == "falcon":       # multi_query: one K/V head; new_decoder_architecture: num_kv_heads groups
         Hkv = int(cfg.get("num_kv_heads") or H) if cfg.get("new_decoder_architecture") else (1 if cfg.get("multi_query", True) else H)
     D = cfg.get("head_dim") or E // H
@@ -166,7 +175,7 @@ def convert(src: str, dst: str, outtype: str = "F16") -> str:
     w.add(f"{a}.attention.head_count", H, ValueType.UINT32)
     w.add(f"{a}.attention.head_count_kv", Hkv, ValueType.UINT32)
     if a in LAYERNORM:
-        w.add(f"{a}.attention.layer_norm_epsilon", float(cfg.get("norm_epsilon") or cfg.get("layer_norm_epsilon") or cfg.get("layer_norm_eps") or 1e-5), ValueType.FLOAT32)
+        w.add(f"{a}.attention.layer_norm_epsilon", float(cfg.get("norm_epsilon") or cfg.get("layer_norm_epsilon") or cfg.get("layer_norm_eps") or cfg.get("norm_eps") or 1e-5), ValueType.FLOAT32)
         if a == "command-r":
             w.add(f"{a}.logit_scale", float(cfg.get("logit_scale", 1.0)), ValueType.FLOAT32)
         if a == "olmo" and cfg.get("clip_qkv"):
@@ -174,7 +183,10 @@ def convert(src: str, dst: str, outtype: str = "F16") -> str:
     else:
         w.add(f"{a}.attention.layer_norm_rms_epsilon", float(cfg.get("rms_norm_eps", 1e-5)), ValueType.FLOAT32)
     w.add(f"{a}.rope.freq_base", theta, ValueType.FLOAT32)
-    w.add(f"{a}.rope.dimension_count", D, ValueType.UINT32)
+    rot = (cfg.get("rotary_pct") or cfg.get("partial_rotary_factor") or rope.get("partial_rotary_factor")) if a in ("gptneox", "stablelm", "nemotron") else None
+    w.add(f"{a}.rope.dimension_count", int(D * float(rot)) if rot else D, ValueType.UINT32)
+    if a == "gptneox":
+        w.add(f"{a}.use_parallel_residual", bool(cfg.get("use_parallel_residual", True)))
     if D * H != E:
         w.add(f"{a}.attention.key_length", D, ValueType.UINT32)
         w.add(f"{a}.attention.value_length", D, ValueType.UINT32)
@@ -253,6 +265,13 @@ def convert(src: str, dst: str, outtype: str = "F16") -> str:
             out = name[len("__moe__."):]
         elif name in TOP_MAP:
             out = TOP_MAP[name]
+        elif a == "gptneox":
+            m = re.match(r"gpt_neox\.layers\.(\d+)\.(.+)", name)
+            if m and m.group(2) in ("attention.bias", "attention.masked_bias", "attention.rotary_emb.inv_freq"):
+                continue
+            if not m or m.group(2) not in NEOX_MAP:
+                raise SystemExit(f"unmapped tensor {name}")
+            out = f"blk.{m.group(1)}.{NEOX_MAP[m.group(2)]}"
         elif a == "falcon":
             m = re.match(r"transformer\.h\.(\d+)\.(.+)", name)
             if not m or m.group(2) not in FALCON_MAP:
@@ -270,6 +289,12 @@ def convert(src: str, dst: str, outtype: str = "F16") -> str:
             # HF groups the rows per K/V head as [that group's query heads..., its key head, its value head]; GGUF wants [all Q | all K | all V]
             g = t.reshape(Hkv, H // Hkv + 2, D, E)
             t = np.concatenate([g[:, :-2].reshape(H * D, E), g[:, -2].reshape(Hkv * D, E), g[:, -1].reshape(Hkv * D, E)], 0)
+        if a == "gptneox" and ".attn_qkv." in out:
+            # HF interleaves per head [q_h | k_h | v_h]; GGUF wants [all Q | all K | all V] (weight rows and bias entries alike)
+            g = t.reshape(H, 3, D, *t.shape[1:])
+            t = np.concatenate([g[:, 0].reshape(H * D, *t.shape[1:]), g[:, 1].reshape(H * D, *t.shape[1:]), g[:, 2].reshape(H * D, *t.shape[1:])], 0)
+        if a == "nemotron" and out.endswith("_norm.weight"):
+            t = t + 1.0          # LayerNorm1p: the checkpoint stores weight - 1
         if a == "seed_oss" and out.endswith("ffn_norm.weight"):
             out = out.replace("ffn_norm.weight", "post_attention_norm.weight")
         if a in PERMUTE_QK and out.endswith("attn_q.weight"):
