@@ -28,7 +28,7 @@ def use_more_bits(i_layer: int, n_layer: int) -> bool:
 
 def tensor_type_for(name: str, ftype: str, i_layer: int, cfg: ModelConfig) -> GGMLType:
     """Per-tensor storage type for a given file type."""
-    if name.endswith("_norm.weight") or name == "rope_freqs.weight" or name.endswith("ffn_gate_inp.weight") \
+    if name.endswith("_norm.weight") or name in ("rope_freqs.weight", "position_embd.weight") or name.endswith("ffn_gate_inp.weight") \
             or name.endswith("ffn_gate_inp_shexp.weight") \
             or name.endswith(".bias"):
         return GGMLType.F32
@@ -120,7 +120,8 @@ def norm_layout(cfg: ModelConfig) -> dict:
         return {"attn": "w", "ffn": "w", "out": "w"}
     return {"starcoder2": {"attn": "wb", "ffn": "wb", "out": "wb"}, "orion": {"attn": "wb", "ffn": "wb", "out": "wb"},
             "gptneox": {"attn": "wb", "ffn": "wb", "out": "wb"}, "stablelm": {"attn": "wb", "ffn": "wb", "out": "wb"},
-            "nemotron": {"attn": "wb", "ffn": "wb", "out": "wb"},
+            "nemotron": {"attn": "wb", "ffn": "wb", "out": "wb"}, "gpt2": {"attn": "wb", "ffn": "wb", "out": "wb"},
+            "starcoder": {"attn": "wb", "ffn": "wb", "out": "wb"}, "codeshell": {"attn": "wb", "ffn": "wb", "out": "wb"},
             "falcon": {"attn": "wb", "ffn": "", "out": "wb"}, "command-r": {"attn": "w", "ffn": "", "out": "w"},
             "olmo": {"attn": "", "ffn": "", "out": ""}}.get(cfg.arch, {"attn": "wb", "ffn": "" if cfg.parallel_residual else "wb", "out": "wb"})
 
@@ -129,11 +130,13 @@ def _tensor_plan(cfg: ModelConfig, rope_freqs: bool):
     """(name, shape, layer, init_std) for every tensor of the architecture; shapes row-major [out, in]."""
     E, F = cfg.n_embd, cfg.n_ff
     nl = norm_layout(cfg)
-    all_bias = cfg.arch in ("starcoder2", "gptneox")       # biases on the attention output and the MLP as well
+    all_bias = cfg.arch in ("starcoder2", "gptneox", "gpt2", "starcoder", "codeshell")       # biases on the attention output and the MLP as well
 
     def norm(name, il, kind):
         return ([(name + ".weight", (E,), il, 0.0)] if "w" in kind else []) + ([(name + ".bias", (E,), il, 0.05)] if "b" in kind else [])
     plan = [("token_embd.weight", (cfg.vocab_size, E), -1, 0.02)]
+    if cfg.learned_pos:
+        plan.append(("position_embd.weight", (cfg.n_ctx_train, E), -1, 0.02))
     if rope_freqs:
         plan.append(("rope_freqs.weight", (cfg.rope_dim // 2,), -1, 0.0))
     for il in range(cfg.n_layer):
@@ -205,7 +208,7 @@ def write_synthetic_gguf(path: str, cfg: ModelConfig, ftype: str = "F16", seed: 
     w.add(f"{a}.context_length", cfg.n_ctx_train, ValueType.UINT32)
     w.add(f"{a}.embedding_length", cfg.n_embd, ValueType.UINT32)
     w.add(f"{a}.block_count", cfg.n_layer, ValueType.UINT32)
-    w.add(f"{a}.feed_forward_length", cfg.n_ff, ValueType.UINT32)
+    w.add(f"{a}.feed_forward_length", cfg.n_ff * (2 if a == "qwen" else 1), ValueType.UINT32)
     w.add(f"{a}.attention.head_count", cfg.n_head, ValueType.UINT32)
     w.add(f"{a}.attention.head_count_kv", cfg.n_head_kv, ValueType.UINT32)
     w.add(f"{a}.attention.layer_norm_epsilon" if cfg.norm_type == "layer" else f"{a}.attention.layer_norm_rms_epsilon", float(cfg.rms_eps), ValueType.FLOAT32)

@@ -64,6 +64,7 @@ class ModelConfig:
 
     # smollm3: every `no_rope_step`-th layer attends without rotary position encoding (`llama.cpp/src/models/smollm3.cpp:26`)
     no_rope_step: int = 0
+    learned_pos: bool = False      # gpt2, starcoder: h = tok_embd[id] + position_embd[pos], no rotary anywhere
 
     @property
     def ffn_norm_name(self) -> str:
@@ -177,6 +178,19 @@ PRESETS: dict[str, ModelConfig] = {
                                  head_dim=64, n_ff=1024, n_ctx_train=512, rope_theta=10000.0, rope_dim=32, rope_neox=True, norm_type="layer", ffn_act="relu2"),
     "tiny-arcee": ModelConfig(name="tiny-arcee", arch="arcee", vocab_size=512, n_embd=256, n_layer=2, n_head=4, n_head_kv=2,
                               head_dim=64, n_ff=1024, n_ctx_train=512, rope_theta=10000.0, rope_dim=64, ffn_act="relu2"),
+    "tiny-gpt2": ModelConfig(name="tiny-gpt2", arch="gpt2", vocab_size=512, n_embd=256, n_layer=2, n_head=4, n_head_kv=4, head_dim=64, n_ff=1024,
+                             n_ctx_train=512, rope_dim=64, rope_neox=True, fused_qkv=True, qkv_bias=True, norm_type="layer", ffn_act="gelu", no_rope_step=1,
+                             learned_pos=True, tie_embeddings=True),
+    "tiny-starcoder": ModelConfig(name="tiny-starcoder", arch="starcoder", vocab_size=512, n_embd=256, n_layer=2, n_head=4, n_head_kv=1, head_dim=64,
+                                  n_ff=1024, n_ctx_train=512, rope_dim=64, rope_neox=True, fused_qkv=True, qkv_bias=True, norm_type="layer", ffn_act="gelu",
+                                  no_rope_step=1, learned_pos=True, tie_embeddings=True),
+    "tiny-codeshell": ModelConfig(name="tiny-codeshell", arch="codeshell", vocab_size=512, n_embd=256, n_layer=2, n_head=4, n_head_kv=2, head_dim=64,
+                                  n_ff=1024, n_ctx_train=512, rope_theta=10000.0, rope_dim=64, rope_neox=True, fused_qkv=True, qkv_bias=True,
+                                  norm_type="layer", ffn_act="gelu"),
+    "tiny-qwen": ModelConfig(name="tiny-qwen", arch="qwen", vocab_size=512, n_embd=256, n_layer=2, n_head=4, n_head_kv=4, head_dim=64, n_ff=512,
+                             n_ctx_train=512, rope_theta=10000.0, rope_dim=64, rope_neox=True, fused_qkv=True, qkv_bias=True),
+    "tiny-baichuan": ModelConfig(name="tiny-baichuan", arch="baichuan", vocab_size=512, n_embd=128, n_layer=32, n_head=2, n_head_kv=2, head_dim=64,
+                                 n_ff=256, n_ctx_train=512, rope_theta=10000.0, rope_dim=64),     # 32 layers: the reference keys the 7B graph on that
     "tiny-command-r": ModelConfig(name="tiny-command-r", arch="command-r", vocab_size=512, n_embd=256, n_layer=2, n_head=4, n_head_kv=2,
                                   head_dim=64, n_ff=512, n_ctx_train=512, rope_theta=10000.0, rope_dim=64, norm_type="layer",
                                   parallel_residual=True, logit_scale=16.0, tie_embeddings=True),
@@ -215,15 +229,19 @@ PRESETS: dict[str, ModelConfig] = {
 #   minicpm, granitemoe - the granite builder (four scalars; granitemoe with routed experts);   smollm3 - no rotation on every 4th layer.
 SUPPORTED_ARCHS = {"llama", "qwen2", "qwen2moe", "qwen3", "qwen3moe", "phi3", "granite",
                    "internlm2", "xverse", "ernie4_5", "exaone", "seed_oss", "minicpm", "granitemoe", "smollm3",
-                   "starcoder2", "falcon", "olmo", "orion", "command-r", "gptneox", "stablelm", "nemotron", "arcee"}
-ROPE_NORM_ARCHS = {"llama", "granite", "granitemoe", "minicpm", "internlm2", "xverse", "ernie4_5", "smollm3", "olmo", "command-r", "arcee"}     # llama_model_rope_type
+                   "starcoder2", "falcon", "olmo", "orion", "command-r", "gptneox", "stablelm", "nemotron", "arcee",
+                   "gpt2", "starcoder", "codeshell", "qwen", "baichuan"}
+ROPE_NORM_ARCHS = {"llama", "granite", "granitemoe", "minicpm", "internlm2", "xverse", "ernie4_5", "smollm3", "olmo", "command-r", "arcee", "baichuan"}     # llama_model_rope_type
 # LayerNorm families and what differs beyond the norm (llama.cpp/src/models/{starcoder2,falcon,olmo,orion,command-r}.cpp):
 #   starcoder2: biases on every matrix, non-gated GELU MLP;  falcon: fused QKV, GELU MLP, attention and MLP in parallel from the same
 #   (or a second) norm;  olmo: norms without parameters;  orion: llama with LayerNorm;  command-r: parallel, logits * logit_scale
 #   gptneox (pythia): fused QKV with bias, rotary on part of each head, GELU MLP with biases, parallel blocks with a second norm for the MLP
 #   stablelm: rotary on part of each head, gated SiLU MLP
 #   nemotron: rotary on part of each head, non-gated ReLU^2 MLP;   arcee keeps RMSNorm but has the same non-gated ReLU^2 MLP
-LAYERNORM_ARCHS = {"starcoder2", "falcon", "olmo", "orion", "command-r", "gptneox", "stablelm", "nemotron"}
+#   gpt2, starcoder (v1): learned position embeddings instead of rotary (starcoder: multi-query), fused QKV, biases everywhere, GELU MLP
+#   codeshell: the same block with rotary.   (qwen v1 and baichuan-7B are RMSNorm / SwiGLU graphs and run the fused path.)
+LAYERNORM_ARCHS = {"starcoder2", "falcon", "olmo", "orion", "command-r", "gptneox", "stablelm", "nemotron", "gpt2", "starcoder", "codeshell"}
+LEARNED_POS_ARCHS = {"gpt2", "starcoder"}
 
 
 def preset(name: str, **overrides) -> ModelConfig:
@@ -265,7 +283,7 @@ def config_from_gguf(meta: dict[str, Any], tensors: dict | None = None) -> Model
                     yarn_beta_fast=float(g("rope.scaling.yarn_beta_fast", 32.0)), yarn_beta_slow=float(g("rope.scaling.yarn_beta_slow", 1.0)))
     tie = tensors is not None and "output.weight" not in tensors
     n_layer = int(g("block_count"))
-    if tensors is not None and "blk.0.ffn_down.weight" in tensors and int(g("feed_forward_length")) != tensors["blk.0.ffn_down.weight"].shape[-1]:
+    if tensors is not None and "blk.0.ffn_down.weight" in tensors and int(g("feed_forward_length")) // (2 if arch == "qwen" else 1) != tensors["blk.0.ffn_down.weight"].shape[-1]:
         raise ValueError(f"{arch}.feed_forward_length = {g('feed_forward_length')} but blk.0.ffn_down.weight has {tensors['blk.0.ffn_down.weight'].shape[-1]} "
                          "input columns: the file's metadata does not describe its tensors")
     # minicpm: defaults of older exports (llama-model.cpp:756-770), overridden by the keys when present
@@ -274,16 +292,17 @@ def config_from_gguf(meta: dict[str, Any], tensors: dict | None = None) -> Model
     return ModelConfig(
         name=str(meta.get("general.name", arch)), arch=arch, vocab_size=int(vocab), n_embd=n_embd,
         n_layer=int(g("block_count")), n_head=n_head, n_head_kv=n_head_kv, head_dim=head_dim,
-        n_ff=int(g("expert_feed_forward_length") or g("feed_forward_length")) if int(g("expert_count", 0) or 0) > 0 else int(g("feed_forward_length")),
+        n_ff=int(g("expert_feed_forward_length") or g("feed_forward_length")) if int(g("expert_count", 0) or 0) > 0
+        else int(g("feed_forward_length")) // (2 if arch == "qwen" else 1),      # qwen v1 files store twice the MLP width (llama-model.cpp: n_ff/2)
         n_ctx_train=int(g("context_length", 2048)),
         rms_eps=float(g("attention.layer_norm_epsilon", 1e-5) if arch in LAYERNORM_ARCHS else g("attention.layer_norm_rms_epsilon", 1e-5)),
-        norm_type="layer" if arch in LAYERNORM_ARCHS else "rms", ffn_act="gelu" if arch in ("starcoder2", "falcon", "gptneox") else "relu2" if arch in ("nemotron", "arcee") else "swiglu",
+        norm_type="layer" if arch in LAYERNORM_ARCHS else "rms", ffn_act="gelu" if arch in ("starcoder2", "falcon", "gptneox", "gpt2", "starcoder", "codeshell") else "relu2" if arch in ("nemotron", "arcee") else "swiglu",
         parallel_residual=arch in ("falcon", "command-r") or (arch == "gptneox" and bool(g("use_parallel_residual", True)))
         or (arch == "stablelm" and tensors is not None and "blk.0.ffn_norm.weight" not in tensors), fused_gate_up=arch == "phi3", rope_theta=float(g("rope.freq_base", 10000.0)),
         rope_dim=int(g("rope.dimension_count", head_dim)), rope_neox=arch not in ROPE_NORM_ARCHS, rope_scale_linear=scale,
         embedding_scale=float(g("embedding_scale") or dflt["embedding_scale"]), residual_scale=float(g("residual_scale") or dflt["residual_scale"]),
         logit_scale=(1.0 / float(g("logit_scale") or 1.0)) if arch == "command-r" else float(g("logit_scale") or dflt["logit_scale"]), attention_scale=float(g("attention.scale", 0.0) or 0.0),
-        no_rope_step=4 if arch == "smollm3" else 0,
+        no_rope_step=4 if arch == "smollm3" else 1 if arch in LEARNED_POS_ARCHS else 0, learned_pos=arch in LEARNED_POS_ARCHS,
         moe_norm_topk=arch != "qwen2moe", n_ff_shared=int(g("expert_shared_feed_forward_length", 0) or 0),
         qkv_bias=arch in ("qwen2", "qwen2moe") or (tensors is not None and ("blk.0.attn_q.bias" in tensors or "blk.0.attn_qkv.bias" in tensors)),
         qk_norm=arch in ("qwen3", "qwen3moe") or (tensors is not None and "blk.0.attn_q_norm.weight" in tensors),

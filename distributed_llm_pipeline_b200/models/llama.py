@@ -559,6 +559,8 @@ class LlamaEngine:
         ops.dequant_rows(self.w.tok_embd, self.tokens[:T] if ids is None else ids, out=self.h[:T])
         if self.cfg.embedding_scale != 1.0:
             self.h[:T].mul_(self.cfg.embedding_scale)
+        if self.w.pos_embd is not None:      # learned absolute positions; self.pos is the device-side position of every batch row
+            self.h[:T].add_(self.w.pos_embd.index_select(0, self.pos[:T].long()))
 
     def _run_layers(self, T: int, attn_fn, fused: bool = False):
         if fused:

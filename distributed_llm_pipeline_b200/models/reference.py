@@ -220,8 +220,11 @@ class ReferenceModel:
         h = h + c.residual_scale * self.ffn(il, self.norm(h, p + c.ffn_norm_name[: -len(".weight")]))
         return h
 
-    def embed(self, tokens: torch.Tensor) -> torch.Tensor:
-        return self.w["token_embd.weight"][tokens] * self.cfg.embedding_scale
+    def embed(self, tokens: torch.Tensor, pos: torch.Tensor | None = None) -> torch.Tensor:
+        h = self.w["token_embd.weight"][tokens] * self.cfg.embedding_scale
+        if self.cfg.learned_pos:        # gpt2, starcoder: learned absolute positions (llama.cpp/src/models/gpt2.cpp:20-25)
+            h = h + self.w["position_embd.weight"][torch.arange(tokens.numel()) if pos is None else pos]
+        return h
 
     def head(self, h: torch.Tensor) -> torch.Tensor:
         c, w = self.cfg, self.w
@@ -246,7 +249,7 @@ class ReferenceModel:
         T = tokens.numel()
         pos = torch.arange(cache.length, cache.length + T)
         layers = range(c.n_layer) if layers is None else layers
-        h = self.embed(tokens) if hidden is None else hidden
+        h = self.embed(tokens, pos) if hidden is None else hidden
         for il in layers:
             h = self.layer(il, h, pos, cache)
         last_stage = len(layers) == 0 or layers[-1] == c.n_layer - 1

@@ -54,6 +54,10 @@ CASES = {
     "nemotron": ("NemotronConfig", "NemotronForCausalLM", {"partial_rotary_factor": 0.5, "norm_eps": 1e-5, "hidden_act": "relu2", "intermediate_size": 1024,
                                                          "attention_bias": False, "mlp_bias": False, "head_dim": 64}),
     "arcee": ("ArceeConfig", "ArceeForCausalLM", {"hidden_act": "relu2", "intermediate_size": 1024, "head_dim": 64, "attention_bias": False, "mlp_bias": False}),
+    "gpt2": ("GPT2Config", "GPT2LMHeadModel", {"n_embd": 256, "n_layer": 2, "n_head": 4, "n_positions": 512, "n_inner": 1024, "activation_function": "gelu_pytorch_tanh",
+                                               "layer_norm_epsilon": 1e-5, "tie_word_embeddings": True}),
+    "starcoder": ("GPTBigCodeConfig", "GPTBigCodeForCausalLM", {"n_embd": 256, "n_layer": 2, "n_head": 4, "n_positions": 512, "n_inner": 1024, "multi_query": True,
+                                                                "activation_function": "gelu_pytorch_tanh", "layer_norm_epsilon": 1e-5, "tie_word_embeddings": True}),
     "olmo": ("OlmoConfig", "OlmoForCausalLM", {"clip_qkv": None, "num_key_value_heads": 4}),
     "command-r": ("CohereConfig", "CohereForCausalLM", {"logit_scale": 0.0625, "layer_norm_eps": 1e-5, "use_qk_norm": False, "tie_word_embeddings": True}),
     "qwen3moe": ("Qwen3MoeConfig", "Qwen3MoeForCausalLM", {"head_dim": 64, "moe_intermediate_size": 128, "num_experts": 4,

@@ -70,7 +70,9 @@ def test_rope_modes():
                                  ("tiny-orion", "F16"), ("tiny-command-r", "F16"),
                                  # rotary on part of each head (the engine re-orders Wq / Wk rows and pads the angle table)
                                  ("tiny-gptneox", "F16"), ("tiny-gptneox", "Q8_0"), ("tiny-stablelm", "F16"),
-                                 ("tiny-nemotron", "F16"), ("tiny-arcee", "F16")])        # non-gated ReLU^2 MLP
+                                 ("tiny-nemotron", "F16"), ("tiny-arcee", "F16"),        # non-gated ReLU^2 MLP
+                                 ("tiny-gpt2", "F16"), ("tiny-starcoder", "F16"),        # learned position embeddings, no rotary
+                                 ("tiny-codeshell", "F16"), ("tiny-qwen", "F16")])
 def test_other_architectures_match_oracle_cpu(tmp_models, key):
     """qwen2 (QKV bias), qwen3 (per-head Q/K norm) and phi3 (fused QKV / gate-up tensors), all with half-split RoPE:
     engine (CPU op fallbacks, paged KV) against the fp32 oracle."""
@@ -96,7 +98,7 @@ def test_other_architectures_match_oracle_cpu(tmp_models, key):
 def test_unknown_architecture_is_rejected():
     from distributed_llm_pipeline_b200.models.config import config_from_gguf
     with pytest.raises(NotImplementedError):
-        config_from_gguf({"general.architecture": "gpt2"})
+        config_from_gguf({"general.architecture": "mamba"})
 
 
 def test_lora_adapter_is_merged_at_load(tmp_models, tmp_path):

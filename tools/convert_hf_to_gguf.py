@@ -26,11 +26,12 @@ ARCHS = {"LlamaForCausalLM": "llama", "MistralForCausalLM": "llama", "MixtralFor
          "Qwen2MoeForCausalLM": "qwen2moe", "Qwen3ForCausalLM": "qwen3", "Qwen3MoeForCausalLM": "qwen3moe", "Phi3ForCausalLM": "phi3", "GraniteForCausalLM": "granite",
          "SmolLM3ForCausalLM": "smollm3", "SeedOssForCausalLM": "seed_oss", "Ernie4_5ForCausalLM": "ernie4_5", "GraniteMoeForCausalLM": "granitemoe",
          "Starcoder2ForCausalLM": "starcoder2", "FalconForCausalLM": "falcon", "OlmoForCausalLM": "olmo", "CohereForCausalLM": "command-r",
-         "GPTNeoXForCausalLM": "gptneox", "StableLmForCausalLM": "stablelm", "NemotronForCausalLM": "nemotron", "ArceeForCausalLM": "arcee"}
+         "GPTNeoXForCausalLM": "gptneox", "StableLmForCausalLM": "stablelm", "NemotronForCausalLM": "nemotron", "ArceeForCausalLM": "arcee",
+         "GPT2LMHeadModel": "gpt2", "GPTBigCodeForCausalLM": "starcoder"}
 # families whose GGUF graph rotates adjacent pairs: HF's half-split Q/K rows are permuted on the way in (ernie4_5 already stores
 # adjacent pairs upstream, so it is not in the list)
 PERMUTE_QK = ("llama", "granite", "granitemoe", "smollm3", "olmo", "arcee")
-LAYERNORM = ("starcoder2", "falcon", "olmo", "command-r", "gptneox", "stablelm", "nemotron")
+LAYERNORM = ("starcoder2", "falcon", "olmo", "command-r", "gptneox", "stablelm", "nemotron", "gpt2", "starcoder")
 LAYER_MAP = {
     "input_layernorm.weight": "attn_norm.weight", "post_attention_layernorm.weight": "ffn_norm.weight",
     "self_attn.q_proj.weight": "attn_q.weight", "self_attn.k_proj.weight": "attn_k.weight", "self_attn.v_proj.weight": "attn_v.weight",
@@ -48,6 +49,10 @@ FALCON_MAP = {"input_layernorm.weight": "attn_norm.weight", "input_layernorm.bia
               "ln_mlp.weight": "attn_norm.weight", "ln_mlp.bias": "attn_norm.bias", "ln_attn.weight": "attn_norm_2.weight", "ln_attn.bias": "attn_norm_2.bias",
               "self_attention.dense.weight": "attn_output.weight", "mlp.dense_h_to_4h.weight": "ffn_up.weight", "mlp.dense_4h_to_h.weight": "ffn_down.weight",
               "self_attention.query_key_value.weight": "attn_qkv.weight"}
+GPT2_MAP = {"ln_1.weight": "attn_norm.weight", "ln_1.bias": "attn_norm.bias", "ln_2.weight": "ffn_norm.weight", "ln_2.bias": "ffn_norm.bias",
+            "attn.c_attn.weight": "attn_qkv.weight", "attn.c_attn.bias": "attn_qkv.bias", "attn.c_proj.weight": "attn_output.weight",
+            "attn.c_proj.bias": "attn_output.bias", "mlp.c_fc.weight": "ffn_up.weight", "mlp.c_fc.bias": "ffn_up.bias",
+            "mlp.c_proj.weight": "ffn_down.weight", "mlp.c_proj.bias": "ffn_down.bias"}
 NEOX_MAP = {"input_layernorm.weight": "attn_norm.weight", "input_layernorm.bias": "attn_norm.bias", "post_attention_layernorm.weight": "ffn_norm.weight",
             "post_attention_layernorm.bias": "ffn_norm.bias", "attention.query_key_value.weight": "attn_qkv.weight", "attention.query_key_value.bias": "attn_qkv.bias",
             "attention.dense.weight": "attn_output.weight", "attention.dense.bias": "attn_output.bias", "mlp.dense_h_to_4h.weight": "ffn_up.weight",
@@ -55,6 +60,7 @@ NEOX_MAP = {"input_layernorm.weight": "attn_norm.weight", "input_layernorm.bias"
 TOP_MAP = {"model.embed_tokens.weight": "token_embd.weight", "model.norm.weight": "output_norm.weight", "lm_head.weight": "output.weight",
            "model.norm.bias": "output_norm.bias", "transformer.word_embeddings.weight": "token_embd.weight",
            "transformer.ln_f.weight": "output_norm.weight", "transformer.ln_f.bias": "output_norm.bias",
+           "transformer.wte.weight": "token_embd.weight", "transformer.wpe.weight": "position_embd.weight",
            "gpt_neox.embed_in.weight": "token_embd.weight", "gpt_neox.final_layer_norm.weight": "output_norm.weight",
            "gpt_neox.final_layer_norm.bias": "output_norm.bias", "embed_out.weight": "output.weight"}
 
@@ -140,6 +146,11 @@ def convert(src: str, dst: str, outtype: str = "F16") -> str:
     if hf_arch not in ARCHS:
         raise SystemExit(f"unsupported architecture {hf_arch}; supported: {sorted(ARCHS)}")
     a = ARCHS[hf_arch]
+    if a in ("gpt2", "starcoder"):       # the GPT-2 config spells its sizes differently
+        cfg = {**cfg, "hidden_size": cfg["n_embd"], "num_hidden_layers": cfg["n_layer"], "num_attention_heads": cfg["n_head"],
+               "intermediate_size": cfg.get("n_inner") or 4 * cfg["n_embd"], "max_position_embeddings": cfg.get("n_positions", 1024),
+               "num_key_value_heads": (1 if cfg.get("multi_query", True) else cfg["n_head"]) if a == "starcoder" else cfg["n_head"],
+               "tie_word_embeddings": cfg.get("tie_word_embeddings", True)}
     E, L = cfg["hidden_size"], cfg["num_hidden_layers"]
     H = cfg["num_attention_heads"]
     Hkv = cfg.get("num_key_value_heads") or H
@@ -265,6 +276,13 @@ def convert(src: str, dst: str, outtype: str = "F16") -> str:
             out = name[len("__moe__."):]
         elif name in TOP_MAP:
             out = TOP_MAP[name]
+        elif a in ("gpt2", "starcoder"):
+            m = re.match(r"transformer\.h\.(\d+)\.(.+)", name)
+            if m and m.group(2) in ("attn.bias", "attn.masked_bias"):
+                continue
+            if not m or m.group(2) not in GPT2_MAP:
+                raise SystemExit(f"unmapped tensor {name}")
+            out = f"blk.{m.group(1)}.{GPT2_MAP[m.group(2)]}"
         elif a == "gptneox":
             m = re.match(r"gpt_neox\.layers\.(\d+)\.(.+)", name)
             if m and m.group(2) in ("attention.bias", "attention.masked_bias", "attention.rotary_emb.inv_freq"):
@@ -285,6 +303,8 @@ def convert(src: str, dst: str, outtype: str = "F16") -> str:
         if name == "lm_head.weight" and cfg.get("tie_word_embeddings"):
             continue
         t = tensors[name].float().numpy()
+        if a == "gpt2" and t.ndim == 2 and out.startswith("blk."):
+            t = t.T             # GPT-2 keeps its projections as Conv1D: [in, out]
         if a == "falcon" and out.endswith("attn_qkv.weight"):
             # HF groups the rows per K/V head as [that group's query heads..., its key head, its value head]; GGUF wants [all Q | all K | all V]
             g = t.reshape(Hkv, H // Hkv + 2, D, E)
@@ -301,7 +321,7 @@ def convert(src: str, dst: str, outtype: str = "F16") -> str:
             t = permute_qk(t, H)
         if a in PERMUTE_QK and out.endswith("attn_k.weight"):
             t = permute_qk(t, Hkv)
-        ttype = qtype if t.ndim >= 2 and not out.endswith("_norm.weight") and not out.endswith("ffn_gate_inp.weight") and not out.endswith("ffn_gate_inp_shexp.weight") else GGMLType.F32
+        ttype = qtype if t.ndim >= 2 and out != "position_embd.weight" and not out.endswith("_norm.weight") and not out.endswith("ffn_gate_inp.weight") and not out.endswith("ffn_gate_inp_shexp.weight") else GGMLType.F32
         if ttype == GGMLType.Q8_0 and t.shape[-1] % 32:
             ttype = GGMLType.F16
         arr = np.ascontiguousarray(t)
