@@ -141,7 +141,8 @@ def _tensor_plan(cfg: ModelConfig, rope_freqs: bool):
         plan.append(("rope_freqs.weight", (cfg.rope_dim // 2,), -1, 0.0))
     for il in range(cfg.n_layer):
         p = f"blk.{il}."
-        plan += norm(p + "attn_norm", il, nl["attn"])
+        if cfg.pre_norm:
+            plan += norm(p + "attn_norm", il, nl["attn"])
         if cfg.fused_qkv:
             plan.append((p + "attn_qkv.weight", (cfg.q_dim + 2 * cfg.kv_dim, E), il, 0.02))
             if cfg.qkv_bias:
@@ -155,12 +156,16 @@ def _tensor_plan(cfg: ModelConfig, rope_freqs: bool):
                      (p + "attn_v.bias", (cfg.kv_dim,), il, 0.05)]
         if cfg.qk_norm:
             plan += [(p + "attn_q_norm.weight", (cfg.head_dim,), il, 0.0), (p + "attn_k_norm.weight", (cfg.head_dim,), il, 0.0)]
+        if cfg.qk_norm_full:
+            plan += [(p + "attn_q_norm.weight", (cfg.q_dim,), il, 0.0), (p + "attn_k_norm.weight", (cfg.kv_dim,), il, 0.0)]
         plan.append((p + "attn_output.weight", (E, cfg.q_dim), il, 0.02))
         if all_bias:
             plan.append((p + "attn_output.bias", (E,), il, 0.05))
+        if cfg.post_norm:
+            plan.append((p + "post_attention_norm.weight", (E,), il, 0.0))
         if cfg.norm_type == "layer":
             plan += norm(p + "ffn_norm", il, nl["ffn"])
-        else:
+        elif cfg.pre_norm:
             plan.append((p + cfg.ffn_norm_name, (E,), il, 0.0))
         if cfg.ffn_act in ("gelu", "relu2"):       # non-gated MLP
             plan += [(p + "ffn_up.weight", (F, E), il, 0.02), (p + "ffn_down.weight", (E, F), il, 0.02)]
@@ -186,6 +191,8 @@ def _tensor_plan(cfg: ModelConfig, rope_freqs: bool):
                 (p + "ffn_down.weight", (E, F), il, 0.02),
                 (p + "ffn_up.weight", (F, E), il, 0.02),
             ]
+        if cfg.post_norm:
+            plan.append((p + "post_ffw_norm.weight", (E,), il, 0.0))
     plan += norm("output_norm", -1, nl["out"])
     if not cfg.tie_embeddings:
         plan.append(("output.weight", (cfg.vocab_size, E), -1, 0.02))

@@ -55,12 +55,17 @@ class ModelConfig:
     norm_type: str = "rms"         # "rms" | "layer" (mean-centred; weight and bias optional per file: olmo has neither)
     ffn_act: str = "swiglu"        # "swiglu" (gated SiLU) | "gelu" | "relu2" (non-gated: ffn_up -> activation -> ffn_down, biases optional)
     parallel_residual: bool = False  # h + attn(n(h)) + ffn(n'(h)) instead of the sequential form (falcon, command-r)
-    fused_gate_up: bool = False    # phi3: ffn_up holds [gate | up]
+    fused_gate_up: bool = False    # phi3, glm4: ffn_up holds [gate | up]
+    # olmo2, glm4: each branch output is normalised before it joins the residual stream (`post_attention_norm`, `post_ffw_norm`);
+    # olmo2 has no norm in front of the branches at all and normalises Q and K over their full width
+    post_norm: bool = False
+    pre_norm: bool = True
+    qk_norm_full: bool = False
 
     @property
     def generic(self) -> bool:
         """True for families that run the unfused layer path (models/llama.py `_layer_generic`)."""
-        return self.norm_type != "rms" or self.ffn_act != "swiglu" or self.parallel_residual
+        return self.norm_type != "rms" or self.ffn_act != "swiglu" or self.parallel_residual or self.post_norm or not self.pre_norm
 
     # smollm3: every `no_rope_step`-th layer attends without rotary position encoding (`llama.cpp/src/models/smollm3.cpp:26`)
     no_rope_step: int = 0
@@ -191,6 +196,10 @@ PRESETS: dict[str, ModelConfig] = {
                              n_ctx_train=512, rope_theta=10000.0, rope_dim=64, rope_neox=True, fused_qkv=True, qkv_bias=True),
     "tiny-baichuan": ModelConfig(name="tiny-baichuan", arch="baichuan", vocab_size=512, n_embd=128, n_layer=32, n_head=2, n_head_kv=2, head_dim=64,
                                  n_ff=256, n_ctx_train=512, rope_theta=10000.0, rope_dim=64),     # 32 layers: the reference keys the 7B graph on that
+    "tiny-olmo2": ModelConfig(name="tiny-olmo2", arch="olmo2", vocab_size=512, n_embd=256, n_layer=2, n_head=4, n_head_kv=2, head_dim=64, n_ff=512,
+                              n_ctx_train=512, rope_theta=10000.0, rope_dim=64, rope_neox=True, post_norm=True, pre_norm=False, qk_norm_full=True),
+    "tiny-glm4": ModelConfig(name="tiny-glm4", arch="glm4", vocab_size=512, n_embd=256, n_layer=2, n_head=4, n_head_kv=2, head_dim=64, n_ff=512,
+                             n_ctx_train=512, rope_theta=10000.0, rope_dim=32, qkv_bias=True, fused_gate_up=True, post_norm=True),
     "tiny-command-r": ModelConfig(name="tiny-command-r", arch="command-r", vocab_size=512, n_embd=256, n_layer=2, n_head=4, n_head_kv=2,
                                   head_dim=64, n_ff=512, n_ctx_train=512, rope_theta=10000.0, rope_dim=64, norm_type="layer",
                                   parallel_residual=True, logit_scale=16.0, tie_embeddings=True),
@@ -230,8 +239,8 @@ PRESETS: dict[str, ModelConfig] = {
 SUPPORTED_ARCHS = {"llama", "qwen2", "qwen2moe", "qwen3", "qwen3moe", "phi3", "granite",
                    "internlm2", "xverse", "ernie4_5", "exaone", "seed_oss", "minicpm", "granitemoe", "smollm3",
                    "starcoder2", "falcon", "olmo", "orion", "command-r", "gptneox", "stablelm", "nemotron", "arcee",
-                   "gpt2", "starcoder", "codeshell", "qwen", "baichuan"}
-ROPE_NORM_ARCHS = {"llama", "granite", "granitemoe", "minicpm", "internlm2", "xverse", "ernie4_5", "smollm3", "olmo", "command-r", "arcee", "baichuan"}     # llama_model_rope_type
+                   "gpt2", "starcoder", "codeshell", "qwen", "baichuan", "olmo2", "glm4"}
+ROPE_NORM_ARCHS = {"llama", "granite", "granitemoe", "minicpm", "internlm2", "xverse", "ernie4_5", "smollm3", "olmo", "command-r", "arcee", "baichuan", "glm4"}     # llama_model_rope_type
 # LayerNorm families and what differs beyond the norm (llama.cpp/src/models/{starcoder2,falcon,olmo,orion,command-r}.cpp):
 #   starcoder2: biases on every matrix, non-gated GELU MLP;  falcon: fused QKV, GELU MLP, attention and MLP in parallel from the same
 #   (or a second) norm;  olmo: norms without parameters;  orion: llama with LayerNorm;  command-r: parallel, logits * logit_scale
@@ -297,15 +306,16 @@ def config_from_gguf(meta: dict[str, Any], tensors: dict | None = None) -> Model
         n_ctx_train=int(g("context_length", 2048)),
         rms_eps=float(g("attention.layer_norm_epsilon", 1e-5) if arch in LAYERNORM_ARCHS else g("attention.layer_norm_rms_epsilon", 1e-5)),
         norm_type="layer" if arch in LAYERNORM_ARCHS else "rms", ffn_act="gelu" if arch in ("starcoder2", "falcon", "gptneox", "gpt2", "starcoder", "codeshell") else "relu2" if arch in ("nemotron", "arcee") else "swiglu",
+        post_norm=arch in ("olmo2", "glm4"), pre_norm=arch != "olmo2", qk_norm_full=arch == "olmo2",
         parallel_residual=arch in ("falcon", "command-r") or (arch == "gptneox" and bool(g("use_parallel_residual", True)))
-        or (arch == "stablelm" and tensors is not None and "blk.0.ffn_norm.weight" not in tensors), fused_gate_up=arch == "phi3", rope_theta=float(g("rope.freq_base", 10000.0)),
+        or (arch == "stablelm" and tensors is not None and "blk.0.ffn_norm.weight" not in tensors), fused_gate_up=arch in ("phi3", "glm4"), rope_theta=float(g("rope.freq_base", 10000.0)),
         rope_dim=int(g("rope.dimension_count", head_dim)), rope_neox=arch not in ROPE_NORM_ARCHS, rope_scale_linear=scale,
         embedding_scale=float(g("embedding_scale") or dflt["embedding_scale"]), residual_scale=float(g("residual_scale") or dflt["residual_scale"]),
         logit_scale=(1.0 / float(g("logit_scale") or 1.0)) if arch == "command-r" else float(g("logit_scale") or dflt["logit_scale"]), attention_scale=float(g("attention.scale", 0.0) or 0.0),
         no_rope_step=4 if arch == "smollm3" else 1 if arch in LEARNED_POS_ARCHS else 0, learned_pos=arch in LEARNED_POS_ARCHS,
         moe_norm_topk=arch != "qwen2moe", n_ff_shared=int(g("expert_shared_feed_forward_length", 0) or 0),
         qkv_bias=arch in ("qwen2", "qwen2moe") or (tensors is not None and ("blk.0.attn_q.bias" in tensors or "blk.0.attn_qkv.bias" in tensors)),
-        qk_norm=arch in ("qwen3", "qwen3moe") or (tensors is not None and "blk.0.attn_q_norm.weight" in tensors),
+        qk_norm=arch in ("qwen3", "qwen3moe") or (arch != "olmo2" and tensors is not None and "blk.0.attn_q_norm.weight" in tensors),
         fused_qkv=arch == "phi3" or (tensors is not None and "blk.0.attn_qkv.weight" in tensors),
         n_expert=int(g("expert_count", 0) or 0), n_expert_used=int(g("expert_used_count", 0) or 0),
         bos_id=int(meta.get("tokenizer.ggml.bos_token_id", 1)), eos_id=int(meta.get("tokenizer.ggml.eos_token_id", 2)),

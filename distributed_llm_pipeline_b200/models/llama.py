@@ -145,8 +145,8 @@ class LlamaEngine:
         self.act = torch.zeros(M, self.F, dtype=f16, device=dev)
         # generic layer path: fp32 MLP pre-activation (bias + GELU run between the two mat-muls), second norm output (falcon-40b)
         self.up32 = torch.zeros(M, self.F, dtype=f32, device=dev) if cfg.ffn_act != "swiglu" else None
-        self.xn2 = torch.zeros(M, self.E, dtype=f16, device=dev) if any(lw.attn_norm2 is not None or (cfg.parallel_residual and lw.ffn_norm is not None)
-                                                                         for lw in weights.layers.values()) else None
+        self.xn2 = torch.zeros(M, self.E, dtype=f16, device=dev) if cfg.post_norm or any(
+            lw.attn_norm2 is not None or (cfg.parallel_residual and lw.ffn_norm is not None) for lw in weights.layers.values()) else None
         self.tokens = torch.zeros(M, dtype=i32, device=dev)
         self.pos = torch.zeros(M, dtype=i32, device=dev)
         self.slot = torch.zeros(M, dtype=i32, device=dev)
@@ -362,7 +362,10 @@ class LlamaEngine:
         lw, cfg, comm = self.w.layers[il], self.cfg, self.comm
         h = self.h[:T]
         tp = comm.tp_size > 1
-        xn = self._norm(h, lw.attn_norm, lw.attn_norm_b, out=self.xn[:T])
+        if cfg.pre_norm:
+            xn = self._norm(h, lw.attn_norm, lw.attn_norm_b, out=self.xn[:T])
+        else:                                                     # olmo2: the branches read the residual stream as it is
+            xn = self.xn[:T].copy_(h)
         xa, xf = xn, xn
         if lw.attn_norm2 is not None:                         # falcon-40b: the attention branch has its own norm of the block input
             xa = self._norm(h, lw.attn_norm2, lw.attn_norm2_b, out=self.xn2[:T])
@@ -374,6 +377,11 @@ class LlamaEngine:
         else:
             ops.linear(lw.wqkv, xa, "f16", out=qkv[:, :lw.wqkv.N], scratch=self._scratch_for(lw.wqkv))
             ops.linear(lw.wv, xa, "f16", out=qkv[:, lw.wqkv.N:], scratch=self._scratch_for(lw.wv))
+        if lw.q_norm_full is not None:                            # olmo2: RMSNorm over the whole Q and K width, before the rotation
+            qd, kd = self.Hq * self.D, self.Hkv * self.D
+            for sl, wn in ((slice(0, qd), lw.q_norm_full), (slice(qd, qd + kd), lw.k_norm_full)):
+                v = qkv[:, sl].float()
+                qkv[:, sl] = (v * torch.rsqrt(v.pow(2).mean(-1, keepdim=True) + cfg.rms_eps) * wn).to(qkv.dtype)
         q = self._rope(il, qkv, T)
         att = attn_fn(il, q, T)
         d = ops.linear(lw.wo, att, "f32", out=self.delta[:T], scratch=self._scratch_for(lw.wo))
@@ -381,7 +389,10 @@ class LlamaEngine:
             d = comm.allreduce_delta(d, il, 0)
         if lw.bo is not None:
             d.add_(lw.bo)
-        if cfg.parallel_residual:       # the MLP reads the norm of the block INPUT: add the attention branch to h only now
+        if cfg.post_norm:               # the attention output is normalised, then joins the residual stream
+            h.add_(self._norm(d, lw.post_attn_norm, None, out=self.xn2[:T]))
+            ffn_in = self._norm(h, lw.ffn_norm, lw.ffn_norm_b, out=self.xn[:T]) if cfg.pre_norm else self.xn[:T].copy_(h)
+        elif cfg.parallel_residual:       # the MLP reads the norm of the block INPUT: add the attention branch to h only now
             h.add_(d)
             ffn_in = xf
         else:
@@ -394,9 +405,12 @@ class LlamaEngine:
         d = ops.linear(lw.w_down, act, "f32", out=self.delta[:T], scratch=self._scratch_for(lw.w_down))
         if tp:
             d = comm.allreduce_delta(d, il, 1)
-        h.add_(d)
         if lw.b_down is not None:
-            h.add_(lw.b_down)
+            d.add_(lw.b_down)
+        if cfg.post_norm:
+            h.add_(self._norm(d, lw.post_ffn_norm, None, out=self.xn2[:T]))
+        else:
+            h.add_(d)
 
     def _layer_fused(self, il: int, T: int, attn_fn):
         """Decode layer with the tensor-parallel all-reduces fused into the mat-vecs (parallel/fused.py):

@@ -142,6 +142,9 @@ class ReferenceModel:
             q, k, v = (self.mm(x, p + f"attn_{n}.weight") for n in "qkv")
         if c.qkv_bias and not c.fused_qkv:    # qwen2 (llama.cpp/src/models/qwen2.cpp)
             q, k, v = (t + w[p + f"attn_{n}.bias"] for t, n in zip((q, k, v), "qkv"))
+        if c.qk_norm_full:    # olmo2: RMSNorm over the whole projected width, before the heads are split
+            q = rms_norm(q, w[p + "attn_q_norm.weight"], c.rms_eps)
+            k = rms_norm(k, w[p + "attn_k_norm.weight"], c.rms_eps)
         q = q.reshape(T, c.n_head, c.head_dim)
         k = k.reshape(T, c.n_head_kv, c.head_dim)
         v = v.reshape(T, c.n_head_kv, c.head_dim)
@@ -216,6 +219,11 @@ class ReferenceModel:
                 return h + self.attention(il, xn, pos, cache) + self.ffn(il, self.norm(h, p + "ffn_norm"))
             xa = self.norm(h, p + "attn_norm_2") if p + "attn_norm_2.weight" in w else xn
             return h + self.attention(il, xa, pos, cache) + self.ffn(il, xn)
+        if c.post_norm:             # olmo2 (no pre-norm) / glm4 (both): the branch output is normalised before the residual add
+            a = self.attention(il, self.norm(h, p + "attn_norm") if c.pre_norm else h, pos, cache)
+            h = h + self.norm(a, p + "post_attention_norm")
+            f = self.ffn(il, self.norm(h, p + "ffn_norm") if c.pre_norm else h)
+            return h + self.norm(f, p + "post_ffw_norm")
         h = h + c.residual_scale * self.attention(il, self.norm(h, p + "attn_norm"), pos, cache)
         h = h + c.residual_scale * self.ffn(il, self.norm(h, p + c.ffn_norm_name[: -len(".weight")]))
         return h

@@ -53,6 +53,10 @@ class LayerWeights:
     bo: torch.Tensor | None = None                     # fp32 [E] attention output bias (added once, after the TP reduction)
     b_up: torch.Tensor | None = None                   # fp32 [local F]
     b_down: torch.Tensor | None = None                 # fp32 [E]
+    post_attn_norm: torch.Tensor | None = None         # olmo2, glm4: norm of each branch output before the residual add
+    post_ffn_norm: torch.Tensor | None = None
+    q_norm_full: torch.Tensor | None = None            # olmo2: RMSNorm weights over the whole Q / K width
+    k_norm_full: torch.Tensor | None = None
 
 
 @dataclass
@@ -241,13 +245,18 @@ def load_weights(src: str | GGUFModelFiles, device, layer_range: range | None = 
 
         def opt(name):
             return f32(name) if name in f else None
-        lw = LayerWeights(attn_norm=norm_w(p + "attn_norm.weight"), wqkv=wqkv, wv=wv_sep,
+        lw = LayerWeights(attn_norm=norm_w(p + "attn_norm.weight") if cfg.pre_norm else None, wqkv=wqkv, wv=wv_sep,
                           wo=mat(p + "attn_output.weight", cols=(hq0 * D, hq1 * D), scale=cfg.residual_scale),
-                          ffn_norm=None if (cfg.parallel_residual and p + cfg.ffn_norm_name not in f) else norm_w(p + cfg.ffn_norm_name))
+                          ffn_norm=None if ((cfg.parallel_residual and p + cfg.ffn_norm_name not in f) or not cfg.pre_norm) else norm_w(p + cfg.ffn_norm_name))
         if cfg.generic:
             lw.attn_norm_b, lw.ffn_norm_b = opt(p + "attn_norm.bias"), opt(p + "ffn_norm.bias")
             lw.attn_norm2, lw.attn_norm2_b = opt(p + "attn_norm_2.weight"), opt(p + "attn_norm_2.bias")
             lw.bo, lw.b_down = opt(p + "attn_output.bias"), opt(p + "ffn_down.bias")
+            lw.post_attn_norm, lw.post_ffn_norm = opt(p + "post_attention_norm.weight"), opt(p + "post_ffw_norm.weight")
+            if cfg.qk_norm_full:
+                if tp_size > 1:
+                    raise NotImplementedError("Q/K norms over the full projected width (olmo2) are not split across tensor-parallel ranks")
+                lw.q_norm_full, lw.k_norm_full = f32(p + "attn_q_norm.weight"), f32(p + "attn_k_norm.weight")
         if cfg.qkv_bias:
             if cfg.fused_qkv:       # gptneox: one bias vector laid out like the fused matrix
                 fb = f32(p + "attn_qkv.bias")

@@ -58,6 +58,8 @@ CASES = {
                                                "layer_norm_epsilon": 1e-5, "tie_word_embeddings": True}),
     "starcoder": ("GPTBigCodeConfig", "GPTBigCodeForCausalLM", {"n_embd": 256, "n_layer": 2, "n_head": 4, "n_positions": 512, "n_inner": 1024, "multi_query": True,
                                                                 "activation_function": "gelu_pytorch_tanh", "layer_norm_epsilon": 1e-5, "tie_word_embeddings": True}),
+    "olmo2": ("Olmo2Config", "Olmo2ForCausalLM", {"num_key_value_heads": 2}),
+    "glm4": ("Glm4Config", "Glm4ForCausalLM", {"partial_rotary_factor": 0.5, "head_dim": 64, "attention_bias": True}),
     "olmo": ("OlmoConfig", "OlmoForCausalLM", {"clip_qkv": None, "num_key_value_heads": 4}),
     "command-r": ("CohereConfig", "CohereForCausalLM", {"logit_scale": 0.0625, "layer_norm_eps": 1e-5, "use_qk_norm": False, "tie_word_embeddings": True}),
     "qwen3moe": ("Qwen3MoeConfig", "Qwen3MoeForCausalLM", {"head_dim": 64, "moe_intermediate_size": 128, "num_experts": 4,

@@ -27,7 +27,7 @@ ARCHS = {"LlamaForCausalLM": "llama", "MistralForCausalLM": "llama", "MixtralFor
          "SmolLM3ForCausalLM": "smollm3", "SeedOssForCausalLM": "seed_oss", "Ernie4_5ForCausalLM": "ernie4_5", "GraniteMoeForCausalLM": "granitemoe",
          "Starcoder2ForCausalLM": "starcoder2", "FalconForCausalLM": "falcon", "OlmoForCausalLM": "olmo", "CohereForCausalLM": "command-r",
          "GPTNeoXForCausalLM": "gptneox", "StableLmForCausalLM": "stablelm", "NemotronForCausalLM": "nemotron", "ArceeForCausalLM": "arcee",
-         "GPT2LMHeadModel": "gpt2", "GPTBigCodeForCausalLM": "starcoder"}
+         "GPT2LMHeadModel": "gpt2", "GPTBigCodeForCausalLM": "starcoder", "Olmo2ForCausalLM": "olmo2", "Glm4ForCausalLM": "glm4"}
 # families whose GGUF graph rotates adjacent pairs: HF's half-split Q/K rows are permuted on the way in (ernie4_5 already stores
 # adjacent pairs upstream, so it is not in the list)
 PERMUTE_QK = ("llama", "granite", "granitemoe", "smollm3", "olmo", "arcee")
@@ -40,6 +40,9 @@ LAYER_MAP = {
     "self_attn.k_norm.weight": "attn_k_norm.weight", "self_attn.qkv_proj.weight": "attn_qkv.weight",
     "mlp.gate_proj.weight": "ffn_gate.weight", "mlp.up_proj.weight": "ffn_up.weight", "mlp.down_proj.weight": "ffn_down.weight",
     "mlp.gate_up_proj.weight": "ffn_up.weight",
+    # olmo2 / glm4: norms behind the branches
+    "post_feedforward_layernorm.weight": "post_ffw_norm.weight", "post_self_attn_layernorm.weight": "post_attention_norm.weight",
+    "post_mlp_layernorm.weight": "post_ffw_norm.weight",
     # LayerNorm families: norm and projection biases, starcoder2's non-gated MLP
     "input_layernorm.bias": "attn_norm.bias", "post_attention_layernorm.bias": "ffn_norm.bias", "self_attn.o_proj.bias": "attn_output.bias",
     "mlp.c_fc.weight": "ffn_up.weight", "mlp.c_fc.bias": "ffn_up.bias", "mlp.c_proj.weight": "ffn_down.weight", "mlp.c_proj.bias": "ffn_down.bias",
@@ -194,7 +197,7 @@ def convert(src: str, dst: str, outtype: str = "F16") -> str:
     else:
         w.add(f"{a}.attention.layer_norm_rms_epsilon", float(cfg.get("rms_norm_eps", 1e-5)), ValueType.FLOAT32)
     w.add(f"{a}.rope.freq_base", theta, ValueType.FLOAT32)
-    rot = (cfg.get("rotary_pct") or cfg.get("partial_rotary_factor") or rope.get("partial_rotary_factor")) if a in ("gptneox", "stablelm", "nemotron") else None
+    rot = (cfg.get("rotary_pct") or cfg.get("partial_rotary_factor") or rope.get("partial_rotary_factor")) if a in ("gptneox", "stablelm", "nemotron", "glm4") else None
     w.add(f"{a}.rope.dimension_count", int(D * float(rot)) if rot else D, ValueType.UINT32)
     if a == "gptneox":
         w.add(f"{a}.use_parallel_residual", bool(cfg.get("use_parallel_residual", True)))
@@ -313,6 +316,8 @@ def convert(src: str, dst: str, outtype: str = "F16") -> str:
             # HF interleaves per head [q_h | k_h | v_h]; GGUF wants [all Q | all K | all V] (weight rows and bias entries alike)
             g = t.reshape(H, 3, D, *t.shape[1:])
             t = np.concatenate([g[:, 0].reshape(H * D, *t.shape[1:]), g[:, 1].reshape(H * D, *t.shape[1:]), g[:, 2].reshape(H * D, *t.shape[1:])], 0)
+        if a == "olmo2":        # no pre-norms: HF's two layer norms are the post-branch ones
+            out = out.replace("ffn_norm.weight", "post_attention_norm.weight")
         if a == "nemotron" and out.endswith("_norm.weight"):
             t = t + 1.0          # LayerNorm1p: the checkpoint stores weight - 1
         if a == "seed_oss" and out.endswith("ffn_norm.weight"):
