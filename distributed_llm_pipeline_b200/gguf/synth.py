@@ -159,7 +159,7 @@ def _tensor_plan(cfg: ModelConfig, rope_freqs: bool):
         if cfg.qk_norm_full:
             plan += [(p + "attn_q_norm.weight", (cfg.q_dim,), il, 0.0), (p + "attn_k_norm.weight", (cfg.kv_dim,), il, 0.0)]
         plan.append((p + "attn_output.weight", (E, cfg.q_dim), il, 0.02))
-        if all_bias:
+        if all_bias or cfg.attn_out_bias:
             plan.append((p + "attn_output.bias", (E,), il, 0.05))
         if cfg.post_norm:
             plan.append((p + "post_attention_norm.weight", (E,), il, 0.0))

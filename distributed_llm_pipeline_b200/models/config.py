@@ -58,6 +58,7 @@ class ModelConfig:
     fused_gate_up: bool = False    # phi3, glm4: ffn_up holds [gate | up]
     # olmo2, glm4: each branch output is normalised before it joins the residual stream (`post_attention_norm`, `post_ffw_norm`);
     # olmo2 has no norm in front of the branches at all and normalises Q and K over their full width
+    attn_out_bias: bool = False    # a bias on the attention output projection (pangu-embedded and the LayerNorm families that carry one)
     post_norm: bool = False
     pre_norm: bool = True
     qk_norm_full: bool = False
@@ -65,7 +66,7 @@ class ModelConfig:
     @property
     def generic(self) -> bool:
         """True for families that run the unfused layer path (models/llama.py `_layer_generic`)."""
-        return self.norm_type != "rms" or self.ffn_act != "swiglu" or self.parallel_residual or self.post_norm or not self.pre_norm
+        return self.norm_type != "rms" or self.ffn_act != "swiglu" or self.parallel_residual or self.post_norm or not self.pre_norm or self.attn_out_bias
 
     # smollm3: every `no_rope_step`-th layer attends without rotary position encoding (`llama.cpp/src/models/smollm3.cpp:26`)
     no_rope_step: int = 0
@@ -200,6 +201,10 @@ PRESETS: dict[str, ModelConfig] = {
                               n_ctx_train=512, rope_theta=10000.0, rope_dim=64, rope_neox=True, post_norm=True, pre_norm=False, qk_norm_full=True),
     "tiny-glm4": ModelConfig(name="tiny-glm4", arch="glm4", vocab_size=512, n_embd=256, n_layer=2, n_head=4, n_head_kv=2, head_dim=64, n_ff=512,
                              n_ctx_train=512, rope_theta=10000.0, rope_dim=32, qkv_bias=True, fused_gate_up=True, post_norm=True),
+    "tiny-mistral3": ModelConfig(name="tiny-mistral3", arch="mistral3", vocab_size=512, n_embd=256, n_layer=2, n_head=4, n_head_kv=2, head_dim=64,
+                                 n_ff=512, n_ctx_train=512, rope_theta=10000.0, rope_dim=64),
+    "tiny-pangu": ModelConfig(name="tiny-pangu", arch="pangu-embedded", vocab_size=512, n_embd=256, n_layer=2, n_head=4, n_head_kv=2, head_dim=64,
+                              n_ff=512, n_ctx_train=512, rope_theta=10000.0, rope_dim=64, rope_neox=True, qkv_bias=True, attn_out_bias=True),
     "tiny-command-r": ModelConfig(name="tiny-command-r", arch="command-r", vocab_size=512, n_embd=256, n_layer=2, n_head=4, n_head_kv=2,
                                   head_dim=64, n_ff=512, n_ctx_train=512, rope_theta=10000.0, rope_dim=64, norm_type="layer",
                                   parallel_residual=True, logit_scale=16.0, tie_embeddings=True),
@@ -239,8 +244,8 @@ PRESETS: dict[str, ModelConfig] = {
 SUPPORTED_ARCHS = {"llama", "qwen2", "qwen2moe", "qwen3", "qwen3moe", "phi3", "granite",
                    "internlm2", "xverse", "ernie4_5", "exaone", "seed_oss", "minicpm", "granitemoe", "smollm3",
                    "starcoder2", "falcon", "olmo", "orion", "command-r", "gptneox", "stablelm", "nemotron", "arcee",
-                   "gpt2", "starcoder", "codeshell", "qwen", "baichuan", "olmo2", "glm4"}
-ROPE_NORM_ARCHS = {"llama", "granite", "granitemoe", "minicpm", "internlm2", "xverse", "ernie4_5", "smollm3", "olmo", "command-r", "arcee", "baichuan", "glm4"}     # llama_model_rope_type
+                   "gpt2", "starcoder", "codeshell", "qwen", "baichuan", "olmo2", "glm4", "mistral3", "pangu-embedded"}
+ROPE_NORM_ARCHS = {"llama", "granite", "granitemoe", "minicpm", "internlm2", "xverse", "ernie4_5", "smollm3", "olmo", "command-r", "arcee", "baichuan", "glm4", "mistral3"}     # llama_model_rope_type
 # LayerNorm families and what differs beyond the norm (llama.cpp/src/models/{starcoder2,falcon,olmo,orion,command-r}.cpp):
 #   starcoder2: biases on every matrix, non-gated GELU MLP;  falcon: fused QKV, GELU MLP, attention and MLP in parallel from the same
 #   (or a second) norm;  olmo: norms without parameters;  orion: llama with LayerNorm;  command-r: parallel, logits * logit_scale
@@ -292,6 +297,8 @@ def config_from_gguf(meta: dict[str, Any], tensors: dict | None = None) -> Model
                     yarn_beta_fast=float(g("rope.scaling.yarn_beta_fast", 32.0)), yarn_beta_slow=float(g("rope.scaling.yarn_beta_slow", 1.0)))
     tie = tensors is not None and "output.weight" not in tensors
     n_layer = int(g("block_count"))
+    if arch == "mistral3" and float(g("attention.temperature_scale", 0.0) or 0.0) != 0.0:
+        raise NotImplementedError("mistral3 checkpoints with a position-dependent attention temperature are not supported")
     if tensors is not None and "blk.0.ffn_down.weight" in tensors and int(g("feed_forward_length")) // (2 if arch == "qwen" else 1) != tensors["blk.0.ffn_down.weight"].shape[-1]:
         raise ValueError(f"{arch}.feed_forward_length = {g('feed_forward_length')} but blk.0.ffn_down.weight has {tensors['blk.0.ffn_down.weight'].shape[-1]} "
                          "input columns: the file's metadata does not describe its tensors")
@@ -306,6 +313,7 @@ def config_from_gguf(meta: dict[str, Any], tensors: dict | None = None) -> Model
         n_ctx_train=int(g("context_length", 2048)),
         rms_eps=float(g("attention.layer_norm_epsilon", 1e-5) if arch in LAYERNORM_ARCHS else g("attention.layer_norm_rms_epsilon", 1e-5)),
         norm_type="layer" if arch in LAYERNORM_ARCHS else "rms", ffn_act="gelu" if arch in ("starcoder2", "falcon", "gptneox", "gpt2", "starcoder", "codeshell") else "relu2" if arch in ("nemotron", "arcee") else "swiglu",
+        attn_out_bias=tensors is not None and "blk.0.attn_output.bias" in tensors and arch not in LAYERNORM_ARCHS,
         post_norm=arch in ("olmo2", "glm4"), pre_norm=arch != "olmo2", qk_norm_full=arch == "olmo2",
         parallel_residual=arch in ("falcon", "command-r") or (arch == "gptneox" and bool(g("use_parallel_residual", True)))
         or (arch == "stablelm" and tensors is not None and "blk.0.ffn_norm.weight" not in tensors), fused_gate_up=arch in ("phi3", "glm4"), rope_theta=float(g("rope.freq_base", 10000.0)),

@@ -18,7 +18,7 @@ PROMPT = [1, 5, 9, 200, 33, 7, 8, 100, 42, 17, 3, 250, 77]
                                  ("tiny-starcoder2", "F16"), ("tiny-starcoder2", "Q8_0"), ("tiny-falcon", "F16"), ("tiny-olmo", "F16"),
                                  ("tiny-orion", "F16"), ("tiny-command-r", "F16"), ("tiny-gptneox", "F16"), ("tiny-gptneox", "Q8_0"), ("tiny-stablelm", "F16"),
                                  ("tiny-nemotron", "F16"), ("tiny-arcee", "F16"), ("tiny-gpt2", "F16"), ("tiny-starcoder", "F16"),
-                                 ("tiny-codeshell", "F16"), ("tiny-qwen", "F16"), ("tiny-olmo2", "F16"), ("tiny-glm4", "F16")])
+                                 ("tiny-codeshell", "F16"), ("tiny-qwen", "F16"), ("tiny-olmo2", "F16"), ("tiny-glm4", "F16"), ("tiny-pangu", "F16")])
 def test_engine_gpu_matches_oracle(tmp_models, key):
     path = tmp_models[key]
     ref = ReferenceModel.from_gguf(path)
