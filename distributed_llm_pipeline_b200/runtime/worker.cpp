@@ -328,7 +328,10 @@ void rmsnorm(const float* x, const float* w, float eps, int T, int E, float* out
 
 // ---- model stage ------------------------------------------------------------------------------------------------------
 struct Hparams { int n_embd, n_layer, n_head, n_head_kv, head_dim, n_ff, n_vocab, n_rot, n_ctx; float eps, theta;
-                 bool neox = false, qkv_bias = false, qk_norm = false, fused_qkv = false; };
+                 bool neox = false, qkv_bias = false, qk_norm = false, fused_qkv = false, fused_gate_up = false;
+                 // granite / minicpm scalars (1 = off): h = embed * emb_scale; h += res_scale * branch; logits /= logit_scale; scores * attn_scale
+                 float emb_scale = 1.f, res_scale = 1.f, logit_scale = 1.f, attn_scale = 0.f;
+                 std::string ffn_norm = "ffn_norm.weight"; };
 
 struct SeqCache { std::vector<std::vector<float>> k, v; int len = 0; };  // per local layer: [n_ctx][Hkv*D]
 
@@ -345,20 +348,32 @@ struct Stage {
     void load(const std::string& path, int a, int b, int n_ctx) {
         g.open(path);
         const std::string ar = g.str.count("general.architecture") ? g.str["general.architecture"] : "llama";
-        if (ar != "llama" && ar != "qwen2" && ar != "qwen3" && ar != "phi3")
-            throw std::runtime_error("the CPU worker runs llama / qwen2 / qwen3 / phi3 checkpoints (got " + ar + ")");
-        hp.neox = ar != "llama";                                   // half-split rotation for the other families
-        hp.qkv_bias = g.has("blk.0.attn_q.bias");                  // qwen2
+        // dense RMSNorm + SwiGLU graphs (the fused-path families of models/config.py without routed experts)
+        static const char* norm_rope[] = {"llama", "granite", "minicpm", "internlm2", "xverse", "ernie4_5", "baichuan", "mistral3"};
+        static const char* neox_rope[] = {"qwen2", "qwen3", "phi3", "exaone", "seed_oss", "qwen"};
+        bool known = false;
+        for (const char* n : norm_rope) if (ar == n) { known = true; hp.neox = false; }
+        for (const char* n : neox_rope) if (ar == n) { known = true; hp.neox = true; }
+        if (!known) throw std::runtime_error("the CPU worker runs dense RMSNorm / SwiGLU checkpoints (llama, granite, minicpm, internlm2, xverse, "
+                                             "ernie4_5, baichuan, mistral3, qwen, qwen2, qwen3, phi3, exaone, seed_oss); got " + ar);
+        hp.qkv_bias = g.has("blk.0.attn_q.bias") || g.has("blk.0.attn_qkv.bias");   // qwen2, seed_oss; qwen: on the fused tensor
         hp.qk_norm = g.has("blk.0.attn_q_norm.weight");            // qwen3
-        hp.fused_qkv = g.has("blk.0.attn_qkv.weight");             // phi3
+        hp.fused_qkv = g.has("blk.0.attn_qkv.weight");             // phi3, qwen
+        hp.fused_gate_up = ar == "phi3";
+        if (ar == "seed_oss") hp.ffn_norm = "post_attention_norm.weight";
         auto N = [&](const char* k, double d) { return g.n(ar + "." + k, d); };
         hp.n_embd = (int)N("embedding_length", 0); hp.n_layer = (int)N("block_count", 0);
         hp.n_head = (int)N("attention.head_count", 0); hp.n_head_kv = (int)N("attention.head_count_kv", hp.n_head);
         hp.head_dim = (int)N("attention.key_length", hp.n_embd / std::max(1, hp.n_head));
-        hp.n_ff = (int)N("feed_forward_length", 0); hp.eps = (float)N("attention.layer_norm_rms_epsilon", 1e-5);
+        hp.n_ff = (int)N("feed_forward_length", 0) / (ar == "qwen" ? 2 : 1); hp.eps = (float)N("attention.layer_norm_rms_epsilon", 1e-5);
         hp.theta = (float)N("rope.freq_base", 10000.0); hp.n_rot = (int)N("rope.dimension_count", hp.head_dim);
         hp.n_vocab = (int)g.get("token_embd.weight").rows();
         hp.n_ctx = n_ctx;
+        if (ar == "minicpm") { hp.emb_scale = 12.f; hp.res_scale = 1.4f / std::sqrt((float)hp.n_layer); hp.logit_scale = 256.f / hp.n_embd; }
+        if (ar == "granite" || ar == "minicpm") {
+            hp.emb_scale = (float)N("embedding_scale", hp.emb_scale); hp.res_scale = (float)N("residual_scale", hp.res_scale);
+            hp.logit_scale = (float)N("logit_scale", hp.logit_scale); hp.attn_scale = (float)N("attention.scale", 0.0);
+        }
         if (N("expert_count", 0) > 0) throw std::runtime_error("MoE checkpoints are not supported by the CPU worker");
         l0 = a; l1 = b < 0 ? hp.n_layer : b;
         if (l0 < 0 || l1 > hp.n_layer || l0 >= l1) throw std::runtime_error("bad layer range");
@@ -437,6 +452,7 @@ struct Stage {
                 if (id < 0 || id >= hp.n_vocab) throw std::runtime_error("token id out of range");
                 decode_row(emb.type, emb.data + (size_t)id * rb, E, h.data() + (size_t)t * E);
             }
+            if (hp.emb_scale != 1.f) for (float& x : h) x *= hp.emb_scale;
         } else {
             if (nbytes != (size_t)T * E * 4) throw std::runtime_error("payload size mismatch (hidden states)");
             memcpy(h.data(), payload, nbytes);
@@ -444,7 +460,13 @@ struct Stage {
         const int qd = Hq * D, kvd = Hkv * D, gqa = Hq / Hkv;
         std::vector<float> xn((size_t)T * E), q((size_t)T * qd), k((size_t)T * kvd), v((size_t)T * kvd), att((size_t)T * qd),
             gate((size_t)T * F), up((size_t)T * F);
-        const float scale = 1.0f / std::sqrt((float)D);
+        const float scale = hp.attn_scale > 0.f ? hp.attn_scale : 1.0f / std::sqrt((float)D);
+        std::vector<float> branch(hp.res_scale != 1.f ? (size_t)T * E : 0);
+        auto add_branch = [&](const Tensor& w, Act& a) {      // h += res_scale * (a . W^T)
+            if (hp.res_scale == 1.f) { matmul(w, a, h.data(), true); return; }
+            matmul(w, a, branch.data());
+            for (size_t i = 0; i < branch.size(); ++i) h[i] += hp.res_scale * branch[i];
+        };
         // rotation angles depend on (position, pair) only: one table per call instead of cos/sin per layer and head
         const int R2 = hp.n_rot / 2;
         std::vector<float> rc((size_t)T * R2), rs((size_t)T * R2);
@@ -471,9 +493,10 @@ struct Stage {
             }
             prof.lap(0);
             if (hp.qkv_bias) {
-                const float* bq = (const float*)g.get(p + "attn_q.bias").data;
-                const float* bk = (const float*)g.get(p + "attn_k.bias").data;
-                const float* bv = (const float*)g.get(p + "attn_v.bias").data;
+                const bool fb = g.has(p + "attn_qkv.bias");       // qwen: one bias laid out like the fused matrix
+                const float* bq = (const float*)g.get(p + (fb ? "attn_qkv.bias" : "attn_q.bias")).data;
+                const float* bk = fb ? bq + qd : (const float*)g.get(p + "attn_k.bias").data;
+                const float* bv = fb ? bq + qd + kvd : (const float*)g.get(p + "attn_v.bias").data;
                 for (int t = 0; t < T; ++t) {
                     for (int i = 0; i < qd; ++i) q[(size_t)t * qd + i] += bq[i];
                     for (int i = 0; i < kvd; ++i) { k[(size_t)t * kvd + i] += bk[i]; v[(size_t)t * kvd + i] += bv[i]; }
@@ -502,14 +525,14 @@ struct Stage {
             prof.lap(1);
             {
                 Act a(att.data(), T, qd);
-                matmul(g.get(p + "attn_output.weight"), a, h.data(), true);
+                add_branch(g.get(p + "attn_output.weight"), a);
             }
             prof.lap(0);
-            rmsnorm(h.data(), (const float*)g.get(p + "ffn_norm.weight").data, hp.eps, T, E, xn.data());
+            rmsnorm(h.data(), (const float*)g.get(p + hp.ffn_norm).data, hp.eps, T, E, xn.data());
             prof.lap(2);
             {
                 Act a(xn.data(), T, E);
-                if (hp.fused_qkv) {   // phi3: ffn_up = [gate | up]
+                if (hp.fused_gate_up) {   // phi3: ffn_up = [gate | up]
                     const Tensor& w = g.get(p + "ffn_up.weight");
                     matmul(slice_rows(w, 0, F), a, gate.data());
                     matmul(slice_rows(w, F, 2 * (uint64_t)F), a, up.data());
@@ -525,7 +548,7 @@ struct Stage {
             prof.lap(4);
             {
                 Act a(gate.data(), T, F);
-                matmul(g.get(p + "ffn_down.weight"), a, h.data(), true);
+                add_branch(g.get(p + "ffn_down.weight"), a);
             }
             prof.lap(0);
         }
@@ -538,6 +561,7 @@ struct Stage {
         rmsnorm(src, (const float*)g.get("output_norm.weight").data, hp.eps, R, E, hn.data());
         Act a(hn.data(), R, E);
         matmul(g.has("output.weight") ? g.get("output.weight") : g.get("token_embd.weight"), a, logits.data());
+        if (hp.logit_scale != 1.f) for (float& x : logits) x /= hp.logit_scale;
         prof.lap(5);
         prof.report(T);
         return logits;

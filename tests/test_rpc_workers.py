@@ -114,9 +114,11 @@ def test_worker_crash_is_healed_by_reconnect_and_replay(tmp_models):
         pool.stop()
 
 
-@pytest.mark.parametrize("key", [("tiny-qwen2", "Q8_0"), ("tiny-qwen3", "F16"), ("tiny-phi3", "Q8_0")])
+@pytest.mark.parametrize("key", [("tiny-qwen2", "Q8_0"), ("tiny-qwen3", "F16"), ("tiny-phi3", "Q8_0"), ("tiny-granite", "Q8_0"), ("tiny-minicpm", "F16"),
+                                 ("tiny-seed-oss", "F16"), ("tiny-qwen", "F16"), ("tiny-exaone", "F16"), ("tiny-internlm2", "F16")])
 def test_other_architectures_on_cpu_workers(tmp_models, key):
-    """qwen2 (bias), qwen3 (per-head Q/K norm), phi3 (fused tensors), all half-split RoPE, through two native stage workers."""
+    """qwen2 (bias), qwen3 (per-head Q/K norm), phi3 (fused tensors), granite / minicpm (four scalars), seed_oss (its own norm tensor name),
+    qwen (fused QKV with bias, separate gate / up), exaone, internlm2 - through two native stage workers."""
     path = tmp_models[key]
     procs, eps = launch_local_workers(path, 2, base_port=_free_ports(1)[0], n_ctx=64, threads=2)
     try:
