@@ -21,6 +21,7 @@ BENCH = [
     Opt(("-n", "--n-gen"), "comma separated generation sizes", "128", str),
     Opt(("-r", "--repetitions"), "repetitions per test", 3, int),
     Opt(("-o", "--output"), "md | json | jsonl | csv | sql", "md", str, choices=("md", "json", "jsonl", "csv", "sql")),
+    Opt(("-d", "--n-depth"), "comma separated context depths: tokens already in the KV cache when a test starts (llama-bench -d)", "0", str),
     Opt(("--batch",), "comma separated decode batch sizes (sequences decoded together)", "1", str),
     Opt(("--microbatches",), "pipeline micro-batches per decode round (0 = one per stage when the batch allows)", 0, int),
 ]
@@ -54,7 +55,8 @@ def main(argv=None):
                      first_stage=grid.first_stage, last_stage=grid.last_stage)
     pps = [int(x) for x in a.n_prompt.split(",") if int(x) > 0]
     gens = [int(x) for x in a.n_gen.split(",") if int(x) > 0]
-    n_ctx = max(pps + [0]) + max(gens + [0]) + 8
+    depths = [max(0, int(x)) for x in str(a.n_depth).split(",")]
+    n_ctx = max(depths) + max(pps + [0]) + max(gens + [0]) + 8
     batches = [max(1, int(x)) for x in str(a.batch).split(",")]
     eng = LlamaEngine(w, n_ctx=max(n_ctx, a.ctx_size), max_seqs=max(batches), page_size=64, max_batch_tokens=max(a.ubatch_size, max(batches), 16),
                       comm=comm, first_stage=grid.first_stage, last_stage=grid.last_stage)
@@ -85,16 +87,26 @@ def main(argv=None):
             eng.free_seq(s)
         return [eng.alloc_seq() for _ in range(n)]
 
-    for n_p in pps:
+    def fill(sid, depth):      # untimed: `depth` tokens of context in front of the measured work (llama-bench.cpp:318,357 `n_depth`)
+        if depth > 0:
+            ctx = torch.randint(3, cfg.vocab_size, (depth,), generator=g, dtype=torch.int32)
+            (stage.prefill(sid, ctx, chunk=a.ubatch_size) if stage else eng.prefill(sid, ctx, chunk=a.ubatch_size))
+
+    for depth in depths:
+      tag = f" @ d{depth}" if depth else ""
+      for n_p in pps:
         ts = []
         for rep in range(a.repetitions + 1):
             sid = fresh(1)[0]
+            fill(sid, depth)
             toks = torch.randint(3, cfg.vocab_size, (n_p,), generator=g, dtype=torch.int32)
             ms = timed(lambda: (stage.prefill(sid, toks, chunk=a.ubatch_size) if stage else eng.prefill(sid, toks, chunk=a.ubatch_size)))
             if rep:
                 ts.append(n_p / ms * 1e3)
-        rows.append({"test": f"pp{n_p}", "n_prompt": n_p, "n_gen": 0, "avg_ts": statistics.mean(ts), "stddev_ts": statistics.pstdev(ts)})
-    for n_g in gens:
+        rows.append({"test": f"pp{n_p}{tag}", "n_prompt": n_p, "n_gen": 0, "n_depth": depth, "avg_ts": statistics.mean(ts), "stddev_ts": statistics.pstdev(ts)})
+    for depth in depths:
+     tag = f" @ d{depth}" if depth else ""
+     for n_g in gens:
       for B in batches:
         # pipeline stages overlap only across micro-batches: a batch is cut into one sequence group per stage (north star:
         # "send/recv overlapped with the next micro-batch's compute"); a single sequence runs the stages serially
@@ -103,6 +115,7 @@ def main(argv=None):
         for rep in range(a.repetitions + 1):
             sids = fresh(B)
             for s in sids:
+                fill(s, depth - 1)
                 (stage.prefill(s, [1]) if stage else eng.prefill(s, [1]))
             first = torch.randint(3, cfg.vocab_size, (B,), generator=g, dtype=torch.int32)
             cut = [B * i // n_mb for i in range(n_mb + 1)]
@@ -120,7 +133,7 @@ def main(argv=None):
             ms = timed(run)
             if rep:
                 ts.append(n_g * B / ms * 1e3)
-        rows.append({"test": f"tg{n_g}" + (f"@b{B}" if B > 1 else ""), "n_prompt": 0, "n_gen": n_g, "batch": B, "microbatches": n_mb,
+        rows.append({"test": f"tg{n_g}" + (f"@b{B}" if B > 1 else "") + tag, "n_prompt": 0, "n_gen": n_g, "n_depth": depth, "batch": B, "microbatches": n_mb,
                      "avg_ts": statistics.mean(ts), "stddev_ts": statistics.pstdev(ts)})
     if grid.rank == 0:
         meta = {"model": os.path.basename(a.model), "params": cfg.n_params(), "size_bytes": w.nbytes(), "pp": grid.pp, "tp": grid.tp,
