@@ -409,8 +409,17 @@ class Orchestrator:
         req = Request(prompt=d.get("prompt", ""), n_predict=n_predict if n_predict > 0 else self.sched.eng.n_ctx,
                       sampling=self._sampling_from(d), stop=stop, cache_prompt=bool(d.get("cache_prompt", True)),
                       ignore_eos=bool(d.get("ignore_eos", False)), n_keep=int(d.get("n_keep", 0)),
-                      n_draft=int(d.get("speculative.n_max", d.get("n_draft", 0)) or 0))
+                      n_draft=int(d.get("speculative.n_max", d.get("n_draft", 0)) or 0),
+                      n_probs=int(d.get("n_probs", 0) or 0) or (int(d.get("logprobs") or 0) if openai else 0))
         rid = "cmpl-" + uuid.uuid4().hex[:24]
+
+        def native_probs(items):      # llama-server `completion_probabilities` (server-task.cpp): one entry per generated token
+            return [{"id": p["id"], "token": p["token"], "logprob": p["logprob"], "top_logprobs": p["top_logprobs"]} for p in items]
+
+        def openai_logprobs(items):   # legacy /v1/completions `logprobs` object
+            return {"tokens": [p["token"] for p in items], "token_logprobs": [p["logprob"] for p in items],
+                    "top_logprobs": [{t["token"]: t["logprob"] for t in p["top_logprobs"]} for p in items]}
+        sent = [0]
         if d.get("stream"):
             writer.write(self._head("200 OK", [("content-type", "text/event-stream"), ("cache-control", "no-cache")] + CORS + [("connection", "close")]))
 
@@ -418,6 +427,12 @@ class Orchestrator:
                 if kind == "token":
                     obj = ({"id": rid, "object": "text_completion", "choices": [{"index": 0, "text": content, "finish_reason": None}]}
                            if openai else {"content": content, "stop": False})
+                    if req.n_probs > 0:           # the entries recorded since the last event (a multi-byte piece may span tokens)
+                        new, sent[0] = req.probs[sent[0]:], len(req.probs)
+                        if openai:
+                            obj["choices"][0]["logprobs"] = openai_logprobs(new)
+                        else:
+                            obj["completion_probabilities"] = native_probs(new)
                     return b"data: " + json.dumps(obj).encode() + b"\n\n"
                 if kind == "done":
                     obj = ({"id": rid, "object": "text_completion", "choices": [{"index": 0, "text": "", "finish_reason": content}]}
@@ -430,12 +445,14 @@ class Orchestrator:
         await self._run_blocking(req)
         if openai:
             await self._json(writer, {"id": rid, "object": "text_completion", "created": int(time.time()), "model": self.info.get("name", "model"),
-                                      "choices": [{"index": 0, "text": req.text, "finish_reason": req.finish_reason}],
+                                      "choices": [{"index": 0, "text": req.text, "finish_reason": req.finish_reason,
+                                                   **({"logprobs": openai_logprobs(req.probs)} if req.n_probs > 0 else {})}],
                                       "usage": {"prompt_tokens": len(req.prompt_ids), "completion_tokens": len(req.output_ids),
                                                 "total_tokens": len(req.prompt_ids) + len(req.output_ids)}})
         else:
             await self._json(writer, {"content": req.text, "stop": True, "stop_type": req.finish_reason, "tokens_predicted": len(req.output_ids),
-                                      "tokens_evaluated": len(req.prompt_ids), "timings": req.timings()})
+                                      "tokens_evaluated": len(req.prompt_ids), "timings": req.timings(),
+                                      **({"completion_probabilities": native_probs(req.probs)} if req.n_probs > 0 else {})})
         return True
 
     async def rerank(self, d: dict, writer) -> bool:
@@ -478,8 +495,14 @@ class Orchestrator:
         sampling = self._sampling_from(d)
         if setup.active and sampling.json_schema is None and not sampling.grammar:
             sampling.json_schema = setup.json_schema         # the generic tool-call envelope (common/chat.cpp, generic handler)
-        req = Request(prompt=prompt, n_predict=n_predict, sampling=sampling, stop=[stop] if isinstance(stop, str) else list(stop))
+        req = Request(prompt=prompt, n_predict=n_predict, sampling=sampling, stop=[stop] if isinstance(stop, str) else list(stop),
+                      n_probs=max(1, int(d.get("top_logprobs") or 0)) if d.get("logprobs") else 0)
         rid = "chatcmpl-" + uuid.uuid4().hex[:24]
+
+        def chat_logprobs(items):     # OpenAI chat `logprobs.content`
+            def ent(t):
+                return {"token": t["token"], "logprob": t["logprob"], "bytes": list(t["token"].encode("utf-8"))}
+            return {"content": [{**ent(p), "top_logprobs": [ent(t) for t in p["top_logprobs"]]} for p in items]}
         model = self.info.get("name", "model")
         if d.get("stream"):
             writer.write(self._head("200 OK", [("content-type", "text/event-stream"), ("cache-control", "no-cache")] + CORS + [("connection", "close")]))
@@ -519,7 +542,8 @@ class Orchestrator:
             if msg.tool_calls:
                 reason = "tool_calls"
         await self._json(writer, {"id": rid, "object": "chat.completion", "created": int(time.time()), "model": model,
-                                  "choices": [{"index": 0, "message": message, "finish_reason": reason}],
+                                  "choices": [{"index": 0, "message": message, "finish_reason": reason,
+                                               **({"logprobs": chat_logprobs(req.probs)} if req.n_probs > 0 else {})}],
                                   "usage": {"prompt_tokens": len(req.prompt_ids), "completion_tokens": len(req.output_ids),
                                             "total_tokens": len(req.prompt_ids) + len(req.output_ids)}, "timings": req.timings()})
         return True

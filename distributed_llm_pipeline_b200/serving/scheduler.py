@@ -40,11 +40,13 @@ class Request:
     ignore_eos: bool = False
     cache_prompt: bool = True
     n_keep: int = 0             # tokens of the prompt that survive a context shift (-1 = the whole prompt)
+    n_probs: int = 0            # > 0: record the log-probability of every generated token and of the n_probs most likely ones
     n_draft: int = 0            # > 0: speculative decoding with prompt-lookup drafts of up to this many tokens (greedy requests)
     id: int = 0
     # filled in by the scheduler
     prompt_ids: list[int] = field(default_factory=list)
     output_ids: list[int] = field(default_factory=list)
+    probs: list[dict] = field(default_factory=list)       # per generated token: {"id", "token", "logprob", "top_logprobs": [...]}
     text: str = ""
     finish_reason: str | None = None
     t_submit: float = 0.0
@@ -347,7 +349,7 @@ class Scheduler:
         normal batched decode step instead (no draft found, sampling is not greedy, engine cannot return all logits)."""
         req = s.req
         n_draft = req.n_draft if req.n_draft > 0 else (self.n_draft_default if req.n_draft == 0 else 0)     # n_draft < 0: off for this request
-        if n_draft <= 0 or not req.sampling.greedy or req.sampling.host_only or not hasattr(self.eng, "copy_seq"):
+        if n_draft <= 0 or req.n_probs > 0 or not req.sampling.greedy or req.sampling.host_only or not hasattr(self.eng, "copy_seq"):
             return False
         from .speculative import ModelDrafter, NgramDrafter
         history = s.cache_tokens + [s.next_token]
@@ -398,11 +400,21 @@ class Scheduler:
 
     def _device_samplable(self, s: Slot) -> bool:
         p = s.req.sampling
-        return not p.host_only and self.eng.device.type == "cuda"
+        return not p.host_only and s.req.n_probs <= 0 and self.eng.device.type == "cuda"
 
     def _sample_rows(self, logits: torch.Tensor, slots: list[Slot]) -> list[int]:
         rows = logits.float().cpu()
-        return [s.sampler.sample(rows[i]) for i, s in enumerate(slots)]
+        out = []
+        for i, s in enumerate(slots):
+            tok = s.sampler.sample(rows[i])
+            if s.req.n_probs > 0:       # `n_probs` / OpenAI `logprobs`: probabilities of the full softmax, before the sampler chain
+                lp = torch.log_softmax(rows[i], -1)      # (server-context.cpp populate_token_probs, post_sampling_probs = false)
+                top = lp.topk(min(s.req.n_probs, lp.numel()))
+                txt = self.tok.token_texts()
+                s.req.probs.append({"id": tok, "token": txt[tok] or "", "logprob": float(lp[tok]),
+                                    "top_logprobs": [{"id": int(j), "token": txt[int(j)] or "", "logprob": float(v)} for v, j in zip(top.values, top.indices)]})
+            out.append(tok)
+        return out
 
     # ---- token acceptance / completion -------------------------------------------------------------------
     def _accept(self, s: Slot, tok: int):

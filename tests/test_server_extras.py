@@ -140,3 +140,35 @@ def test_rerank_route(server):
     assert d["results"][0]["relevance_score"] >= d["results"][1]["relevance_score"] and d["results"][0]["document"]["text"] == docs[0]
     status, _ = _http(server, "POST", "/rerank", json.dumps({"query": "x"}).encode())
     assert "400" in status
+
+
+def test_token_probabilities_on_every_route(server):
+    """`n_probs` on /completion, `logprobs` on /v1/completions, `logprobs` + `top_logprobs` on /v1/chat/completions, streamed or not:
+    log-probabilities of the full softmax, the sampled token's own entry consistent with the candidates listed."""
+    import math
+    body = {"prompt": "the quick brown", "n_predict": 5, "temperature": 0, "n_probs": 3, "cache_prompt": False}
+    status, payload = _http(server, "POST", "/completion", json.dumps(body).encode())
+    d = json.loads(payload)
+    cp = d["completion_probabilities"]
+    assert len(cp) == d["tokens_predicted"] == 5
+    for e in cp:
+        assert len(e["top_logprobs"]) == 3 and e["top_logprobs"][0]["logprob"] >= e["top_logprobs"][1]["logprob"] >= e["top_logprobs"][2]["logprob"]
+        assert e["logprob"] <= 0 and e["id"] == e["top_logprobs"][0]["id"]          # greedy: the sampled token is the most likely one
+        assert sum(math.exp(t["logprob"]) for t in e["top_logprobs"]) <= 1.0 + 1e-5
+    # the same request without probabilities gives the same text (the host path samples like the device path at temperature 0)
+    plain = json.loads(_http(server, "POST", "/completion", json.dumps({**body, "n_probs": 0}).encode())[1])
+    assert plain["content"] == d["content"] and "completion_probabilities" not in plain
+    # streamed: the entries arrive with the token events and add up to the same list
+    status, payload = _http(server, "POST", "/completion", json.dumps({**body, "stream": True}).encode())
+    events = [json.loads(l[6:]) for l in payload.decode().split("\n") if l.startswith("data: {")]
+    streamed = [p for e in events for p in e.get("completion_probabilities", [])]
+    assert [p["id"] for p in streamed] == [p["id"] for p in cp]
+    # OpenAI dialects
+    o = json.loads(_http(server, "POST", "/v1/completions", json.dumps({"prompt": "the quick brown", "max_tokens": 4, "temperature": 0, "logprobs": 2}).encode())[1])
+    lp = o["choices"][0]["logprobs"]
+    assert len(lp["tokens"]) == len(lp["token_logprobs"]) == len(lp["top_logprobs"]) == 4 and all(len(t) <= 2 for t in lp["top_logprobs"])
+    c = json.loads(_http(server, "POST", "/v1/chat/completions", json.dumps({"messages": [{"role": "user", "content": "hi"}], "max_tokens": 3, "temperature": 0,
+                                                                              "logprobs": True, "top_logprobs": 2}).encode())[1])
+    content = c["choices"][0]["logprobs"]["content"]
+    assert len(content) == 3 and all(len(e["top_logprobs"]) == 2 and e["bytes"] == list(e["token"].encode()) for e in content)
+    assert "logprobs" not in json.loads(_http(server, "POST", "/v1/chat/completions", json.dumps({"messages": [{"role": "user", "content": "hi"}], "max_tokens": 2}).encode())[1])["choices"][0]
