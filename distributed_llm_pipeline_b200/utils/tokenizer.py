@@ -24,6 +24,59 @@ LLAMA3_PAT = (r"(?i:'s|'t|'re|'ve|'m|'ll|'d)|[^\r\n\p{L}\p{N}]?\p{L}+|\p{N}{1,3}
               r"\s+(?!\S)|\s+")
 
 
+# Pre-tokenizers by `tokenizer.ggml.pre` (`llama.cpp/src/llama-vocab.cpp:279-480` picks the same expressions per name; they are the split
+# rules of each family's own tokenizer.json).  Every expression of a list is applied in turn to the pieces produced by the one before;
+# matches and the text between matches are both kept as pieces (`unicode_regex_split`).
+_CONTR = r"(?:'[sS]|'[tT]|'[rR][eE]|'[vV][eE]|'[mM]|'[lL][lL]|'[dD])"
+_GPT2_CORE = r"""'s|'t|'re|'ve|'m|'ll|'d| ?\p{L}+| ?\p{N}+| ?[^\s\p{L}\p{N}]+|\s+(?!\S)"""
+_CJK = "[\u4e00-\u9fa5\u3040-\u309f\u30a0-\u30ff]+"
+PRE_TOKENIZERS: dict[str, list[str]] = {
+    "default": [GPT2_PAT],
+    "llama-bpe": [LLAMA3_PAT],
+    "gpt-2": [_GPT2_CORE],
+    "qwen2": [_CONTR + r"|[^\r\n\p{L}\p{N}]?\p{L}+|\p{N}| ?[^\s\p{L}\p{N}]+[\r\n]*|\s*[\r\n]+|\s+(?!\S)|\s+"],
+    "chatglm-bpe": [_CONTR + r"|[^\r\n\p{L}\p{N}]?\p{L}+|\p{N}{1,3}| ?[^\s\p{L}\p{N}]+[\r\n]*|\s*[\r\n]+|\s+(?!\S)|\s+"],
+    "seed-coder": [_CONTR + r"|[^\r\n\p{L}\p{N}]?\p{L}+|\p{N}{1}| ?[^\s\p{L}\p{N}\r\n]+|\s*[\r\n]+|\s+(?!\S)|\s+"],
+    "starcoder": [r"\p{N}", _GPT2_CORE],
+    "falcon": [r"[\p{P}\$\+<=>\^~\|`]+", _GPT2_CORE, "[0-9][0-9][0-9]"],
+    "deepseek-coder": ["[\r\n]", r"\s?\p{L}+", r"\s?\p{P}+", "[\u4e00-\u9fa5\u0800-\u4e00\uac00-\ud7ff]+", r"\p{N}"],
+    "deepseek-v3": [r"\p{N}{1,3}", _CJK,
+                    r"[!\"#$%&'()*+,\-./:;<=>?@\[\\\]^_`{|}~][A-Za-z]+|[^\r\n\p{L}\p{P}\p{S}]?[\p{L}\p{M}]+| ?[\p{P}\p{S}]+[\r\n]*|\s*[\r\n]+|\s+(?!\S)|\s+"],
+    "bloom": [r" ?[^(\s|.,!?…。，、।۔،)]+"],
+    "viking": [r" ?[^(\s|.,!?…。，、।۔،)]+", r"\p{N}"],
+    "tekken": [r"[^\r\n\p{L}\p{N}]?((?=[\p{L}])([^a-z]))*((?=[\p{L}])([^A-Z]))+|[^\r\n\p{L}\p{N}]?((?=[\p{L}])([^a-z]))+((?=[\p{L}])([^A-Z]))*|\p{N}| ?[^\s\p{L}\p{N}]+[\r\n/]*|\s*[\r\n]+|\s+(?!\S)|\s+"],
+    "gpt-4o": [r"[^\r\n\p{L}\p{N}]?((?=[\p{L}])([^a-z]))*((?=[\p{L}])([^A-Z]))+" + _CONTR + r"?|[^\r\n\p{L}\p{N}]?((?=[\p{L}])([^a-z]))+((?=[\p{L}])([^A-Z]))*" + _CONTR
+               + r"?|\p{N}{1,3}| ?[^\s\p{L}\p{N}]+[\r\n/]*|\s*[\r\n]+|\s+(?!\S)|\s+"],
+}
+for _name, _same in (("llama3", "llama-bpe"), ("llama-v3", "llama-bpe"), ("dbrx", "llama-bpe"), ("smaug-bpe", "llama-bpe"),
+                     ("mpt", "gpt-2"), ("olmo", "gpt-2"), ("jais", "gpt-2"), ("phi-2", "gpt-2"), ("exaone4", "gpt-2"), ("roberta-bpe", "gpt-2"), ("gigachat", "gpt-2"),
+                     ("stablelm2", "qwen2"), ("deepseek-r1-qwen", "qwen2"), ("hunyuan", "qwen2"), ("megrez", "qwen2"), ("grok-2", "qwen2"),
+                     ("glm4", "chatglm-bpe"), ("refact", "starcoder"), ("command-r", "starcoder"), ("smollm", "starcoder"), ("codeshell", "starcoder"),
+                     ("exaone", "starcoder"), ("minerva-7b", "starcoder"), ("poro-chat", "bloom"), ("gpt3-finnish", "bloom"), ("llama4", "gpt-4o"),
+                     ("minimax-m2", "gpt-4o"), ("deepseek3-llm", "deepseek-v3"), ("hunyuan-dense", "deepseek-v3")):
+    PRE_TOKENIZERS[_name] = PRE_TOKENIZERS[_same]
+IGNORE_MERGES = {"llama-bpe", "llama3", "llama-v3", "tekken"}       # a word that is itself a token is taken whole (llama-vocab.cpp `ignore_merges`)
+
+
+def pre_split(text: str, exprs) -> list[str]:
+    pieces = [text]
+    for rx in exprs:
+        nxt: list[str] = []
+        for p in pieces:
+            last = 0
+            for m in rx.finditer(p):
+                if m.end() == m.start():
+                    continue
+                if m.start() > last:
+                    nxt.append(p[last:m.start()])
+                nxt.append(m.group(0))
+                last = m.end()
+            if last < len(p):
+                nxt.append(p[last:])
+        pieces = nxt
+    return pieces
+
+
 @lru_cache(maxsize=1)
 def _bytes_to_unicode() -> dict[int, str]:
     bs = list(range(ord("!"), ord("~") + 1)) + list(range(0xA1, 0xAC + 1)) + list(range(0xAE, 0xFF + 1))
@@ -80,8 +133,10 @@ class Tokenizer:
         else:
             merges = meta.get("tokenizer.ggml.merges", [])
             self.ranks = {tuple(m.split(" ", 1)): i for i, m in enumerate(merges)}
-            pre = meta.get("tokenizer.ggml.pre", "default")
-            self.pat = re.compile(LLAMA3_PAT if pre in ("llama-bpe", "llama3", "llama-v3") else GPT2_PAT)
+            pre = str(meta.get("tokenizer.ggml.pre", "default"))
+            self.pre = pre if pre in PRE_TOKENIZERS else "default"
+            self.pre_exprs = [re.compile(e) for e in PRE_TOKENIZERS[self.pre]]
+            self.ignore_merges = pre in IGNORE_MERGES
             self.b2u = _bytes_to_unicode()
             self.u2b = {u: b for b, u in self.b2u.items()}
         self.special = {t: i for i, t in enumerate(self.tokens) if self.types[i] in (TokenType.CONTROL, TokenType.USER_DEFINED) and len(t) > 1}
@@ -162,8 +217,11 @@ class Tokenizer:
             t = text.replace(" ", SPM_SPACE)
             return self._spm_encode(t)
         out: list[int] = []
-        for m in self.pat.findall(text):
+        for m in pre_split(text, self.pre_exprs):
             word = "".join(self.b2u[b] for b in m.encode("utf-8"))
+            if self.ignore_merges and word in self.tok2id:
+                out.append(self.tok2id[word])
+                continue
             for piece in self._bpe_word(word):
                 tid = self.tok2id.get(piece)
                 if tid is not None:
