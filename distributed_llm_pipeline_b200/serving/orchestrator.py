@@ -57,37 +57,22 @@ def _render_jinja(tmpl: str, messages: list[dict], meta: dict) -> str | None:
 
 
 def apply_chat_template(meta: dict, messages: list[dict]) -> str:
-    """Minimal chat formatting: Llama-3 and ChatML families are recognised from the GGUF template string; models without a
-    template (random-init checkpoints) get the plain concatenation.  (ref: built-in templates, `llama.cpp/src/llama-chat.cpp`)"""
+    """Chat formatting, in the reference's order of preference (`common/chat.cpp`, `llama-chat.cpp`): a built-in format forced by name
+    (`--chat-template NAME` -> `meta["dlp.chat_template_name"]`), the model's own Jinja template rendered in a sandbox, the built-in
+    format its template text is recognised as (`serving/chat_templates.py`: 46 formats, each checked against the reference's output), and
+    for checkpoints without any template (random-init ones) the plain concatenation."""
+    from . import chat_templates
+    name = meta.get("dlp.chat_template_name")
+    if name:
+        return chat_templates.apply(str(name), messages)
     tmpl = str(meta.get("tokenizer.chat_template", ""))
     rendered = _render_jinja(tmpl, messages, meta) if "{%" in tmpl or "{{" in tmpl else None
     if rendered is not None:
         return rendered
-    if "<|start_header_id|>" in tmpl:
-        out = "".join(f"<|start_header_id|>{m['role']}<|end_header_id|>\n\n{m['content']}<|eot_id|>" for m in messages)
-        return out + "<|start_header_id|>assistant<|end_header_id|>\n\n"
-    if "<|im_start|>" in tmpl:
-        out = "".join(f"<|im_start|>{m['role']}\n{m['content']}<|im_end|>\n" for m in messages)
-        return out + "<|im_start|>assistant\n"
-    if "<start_of_turn>" in tmpl:      # gemma
-        out = "".join(f"<start_of_turn>{'model' if m['role'] == 'assistant' else 'user'}\n{m['content']}<end_of_turn>\n" for m in messages)
-        return out + "<start_of_turn>model\n"
-    if "<|assistant|>" in tmpl and "<|end|>" in tmpl:   # phi-3
-        return "".join(f"<|{m['role']}|>\n{m['content']}<|end|>\n" for m in messages) + "<|assistant|>\n"
-    if "<|assistant|>" in tmpl:        # zephyr
-        return "".join(f"<|{m['role']}|>\n{m['content']}</s>\n" for m in messages) + "<|assistant|>\n"
-    if "[INST]" in tmpl:
-        out, sys_txt = "", ""
-        for m in messages:
-            if m["role"] == "system":      # llama-2 style: the system text rides inside the first [INST] block
-                sys_txt = f"<<SYS>>\n{m['content']}\n<</SYS>>\n\n" if "<<SYS>>" in tmpl else m["content"] + "\n\n"
-            elif m["role"] == "user":
-                out += f"[INST] {sys_txt}{m['content']} [/INST]"
-                sys_txt = ""
-            else:
-                out += f" {m['content']}</s>"
-        return out
-    return "\n".join(m["content"] for m in messages)
+    detected = chat_templates.detect(tmpl) if tmpl else None
+    if detected:
+        return chat_templates.apply(detected, messages)
+    return "\n".join(m["content"] if isinstance(m.get("content"), str) else "" for m in messages)
 
 
 class Orchestrator:
@@ -898,6 +883,7 @@ def main(argv=None):
     ap.add_argument("--max-queue", type=int, default=0, help="answer 503 once this many requests are waiting (0 = unbounded)")
     ap.add_argument("--slot-save-path", default=None, help="directory for /slots/{id}?action=save|restore files")
     ap.add_argument("--context-shift", action="store_true", help="slide the context window instead of stopping at n_ctx")
+    ap.add_argument("--chat-template", default=None, help="built-in chat format by name instead of the model's own template (chatml, llama3, mistral-v7, gemma, ...)")
     add_parallel_args(ap)
     a = ap.parse_args(argv)
     maybe_reexec(a, "distributed_llm_pipeline_b200.serving.orchestrator", argv)
@@ -922,6 +908,11 @@ def main(argv=None):
     for l in logs:
         sys.stderr.write(l)
     sched.context_shift = a.context_shift
+    if a.chat_template:
+        from . import chat_templates
+        if a.chat_template not in chat_templates.names():
+            ap.error(f"--chat-template: unknown name {a.chat_template!r}; built-in: {', '.join(chat_templates.names())}")
+        info.setdefault("metadata", {})["dlp.chat_template_name"] = a.chat_template
     sched.start()
     orch = Orchestrator(sched, info, a.static, a.predict, logs, api_key=a.api_key, max_queue=a.max_queue, slot_save_path=a.slot_save_path)
     print(f"dlp_b200 orchestrator ready: http://localhost:{a.port}", flush=True)
