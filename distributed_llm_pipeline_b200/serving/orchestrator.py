@@ -60,7 +60,7 @@ def apply_chat_template(meta: dict, messages: list[dict]) -> str:
     """Chat formatting, in the reference's order of preference (`common/chat.cpp`, `llama-chat.cpp`): a built-in format forced by name
     (`--chat-template NAME` -> `meta["dlp.chat_template_name"]`), the model's own Jinja template rendered in a sandbox, the built-in
     format its template text is recognised as (`serving/chat_templates.py`: 46 formats, each checked against the reference's output), and
-    for checkpoints without any template (random-init ones) the plain concatenation."""
+    for checkpoints without any template ChatML, which is what the reference server falls back to (`common_chat_templates_init`)."""
     from . import chat_templates
     name = meta.get("dlp.chat_template_name")
     if name:
@@ -72,7 +72,7 @@ def apply_chat_template(meta: dict, messages: list[dict]) -> str:
     detected = chat_templates.detect(tmpl) if tmpl else None
     if detected:
         return chat_templates.apply(detected, messages)
-    return "\n".join(m["content"] if isinstance(m.get("content"), str) else "" for m in messages)
+    return chat_templates.apply("chatml", messages)
 
 
 class Orchestrator:
@@ -227,8 +227,25 @@ class Orchestrator:
                 await self._json(writer, self.sched.slots_info())
                 return True
             if method == "GET" and path == "/props":
-                await self._json(writer, {"model": self.info, "total_slots": self.sched.n_slots, "n_ctx": self.sched.eng.n_ctx,
-                                          "uptime_s": round(time.time() - self.t_start, 1)})
+                from .sampler import SamplingParams
+                dp = SamplingParams()       # what a request gets when it names nothing (llama-server: `default_generation_settings`)
+                md = self.info.get("metadata", {})
+                await self._json(writer, {
+                    "default_generation_settings": {"n_ctx": self.sched.eng.n_ctx, "params": {
+                        "seed": dp.seed, "temperature": dp.temperature, "dynatemp_range": dp.dynatemp_range, "dynatemp_exponent": dp.dynatemp_exponent,
+                        "top_k": dp.top_k, "top_p": dp.top_p, "min_p": dp.min_p, "top_n_sigma": dp.top_n_sigma, "xtc_probability": dp.xtc_probability,
+                        "xtc_threshold": dp.xtc_threshold, "typical_p": dp.typical_p, "repeat_last_n": dp.repeat_last_n, "repeat_penalty": dp.repeat_penalty,
+                        "presence_penalty": dp.presence_penalty, "frequency_penalty": dp.frequency_penalty, "dry_multiplier": dp.dry_multiplier,
+                        "dry_base": dp.dry_base, "dry_allowed_length": dp.dry_allowed_length, "dry_penalty_last_n": dp.dry_penalty_last_n,
+                        "mirostat": dp.mirostat, "mirostat_tau": dp.mirostat_tau, "mirostat_eta": dp.mirostat_eta, "n_predict": self.n_predict,
+                        "max_tokens": self.n_predict, "n_keep": 0, "ignore_eos": False, "stream": False, "n_probs": 0,
+                        "speculative.n_max": getattr(self.sched, "n_draft_default", 0)}},
+                    "total_slots": self.sched.n_slots, "model_alias": self.info.get("name", "model"), "model_path": self.info.get("path", self.info.get("name", "")),
+                    "modalities": {"vision": False, "audio": False}, "endpoint_slots": True, "endpoint_props": False, "endpoint_metrics": True,
+                    "chat_template": md.get("tokenizer.chat_template", ""), "bos_token": md.get("bos_token", ""), "eos_token": md.get("eos_token", ""),
+                    "build_info": "dlp_b200", "is_sleeping": False,
+                    # this server's own fields
+                    "model": self.info, "n_ctx": self.sched.eng.n_ctx, "uptime_s": round(time.time() - self.t_start, 1)})
                 return True
             if method == "GET" and path == "/v1/models":
                 await self._json(writer, {"object": "list", "data": [{"id": self.info.get("name", "model"), "object": "model",

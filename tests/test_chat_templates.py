@@ -82,4 +82,4 @@ def test_orchestrator_formatter_prefers_name_then_jinja_then_detection():
     jinja = "{% for m in messages %}<{{ m.role }}>{{ m.content }}{% endfor %}<assistant>"
     assert apply_chat_template({"tokenizer.chat_template": jinja}, msgs) == "<user>Hello<assistant>Hi there<user>Bye<assistant>"
     assert apply_chat_template({"tokenizer.chat_template": "uses <|start_header_id|> and <|eot_id|>"}, msgs) == REF["llama3"]["nosys"]
-    assert apply_chat_template({}, msgs) == "Hello\nHi there\nBye"
+    assert apply_chat_template({}, msgs) == REF["chatml"]["nosys"]         # no template at all: ChatML, like the reference server

@@ -242,7 +242,7 @@ def test_api_key_slot_save_restore_and_templates(tmp_models, tmp_path):
         d = json.loads(out)
         assert d["content"] == first and d["timings"]["cache_n"] > 0
         _, _, out = _http(port, "POST", "/apply-template", json.dumps({"messages": [{"role": "user", "content": "hi"}]}).encode(), auth)
-        assert json.loads(out)["prompt"] == "hi"
+        assert json.loads(out)["prompt"] == "<|im_start|>user\nhi<|im_end|>\n<|im_start|>assistant\n"      # no template in the file: ChatML, like llama-server
         st, _, _ = _http(port, "POST", "/infill", json.dumps({"input_prefix": "a", "input_suffix": "b"}).encode(), auth)
         assert " 501 " in st                                             # synthetic vocab has no FIM tokens
     finally:

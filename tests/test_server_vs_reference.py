@@ -1,0 +1,157 @@
+"""The HTTP API side by side with the reference's `llama-server` (unmodified, CPU back-end) on the same tiny checkpoint: tokenisation,
+greedy completions with token probabilities, logit bias, grammar-constrained decoding, stop strings, the OpenAI dialect's envelope.
+(llama.cpp/tools/server/server.cpp routes :164-197; tests of the same behaviours: tools/server/tests/unit/test_completion.py, test_tokenize.py)"""
+import asyncio
+import json
+import os
+import socket
+import subprocess
+import sys
+import threading
+import time
+import urllib.request
+
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+from baseline import reference as ref_build  # noqa: E402
+
+from distributed_llm_pipeline_b200.serving.orchestrator import Orchestrator, build_service  # noqa: E402
+
+
+def _free_port():
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    p = s.getsockname()[1]
+    s.close()
+    return p
+
+
+def _post(port, path, body):
+    r = urllib.request.urlopen(urllib.request.Request(f"http://127.0.0.1:{port}{path}", json.dumps(body).encode(), {"Content-Type": "application/json"}), timeout=120)
+    return json.loads(r.read())
+
+
+def _get(port, path):
+    return json.loads(urllib.request.urlopen(f"http://127.0.0.1:{port}{path}", timeout=30).read())
+
+
+@pytest.fixture(scope="module")
+def pair(tmp_models, tmp_path_factory):
+    why = ref_build.ensure(allow_build=False)
+    if why is not None or not ref_build.have("llama-server"):
+        pytest.skip(f"reference binaries unavailable: {why}")
+    model = tmp_models[("tiny", "F16")]
+    env = ref_build.cpu_env(str(tmp_path_factory.mktemp("refsrv")))
+    rp = _free_port()
+    proc = subprocess.Popen([ref_build.exe("llama-server"), "-m", model, "-ngl", "0", "-c", "512", "-np", "2", "--host", "127.0.0.1", "--port", str(rp), "-t", "4",
+                             "--no-warmup"], env=env, stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL)
+    for _ in range(200):
+        try:
+            _get(rp, "/health")
+            break
+        except Exception:
+            time.sleep(0.1)
+    else:
+        proc.terminate()
+        pytest.skip("the reference server did not come up here")
+    sched, info, logs = build_service(model, device="cpu", n_ctx=512, n_slots=2, n_batch=64)
+    sched.start()
+    orch = Orchestrator(sched, info, n_predict=16, startup_logs=logs)
+    op = _free_port()
+    loop = asyncio.new_event_loop()
+    threading.Thread(target=lambda: loop.run_until_complete(orch.serve("127.0.0.1", op)), daemon=True).start()
+    for _ in range(100):
+        try:
+            socket.create_connection(("127.0.0.1", op), timeout=0.2).close()
+            break
+        except OSError:
+            time.sleep(0.05)
+    yield op, rp
+    sched.stop()
+    proc.terminate()
+    proc.wait()
+
+
+TEXTS = ["hello there world", "The quick brown fox jumps over 13 lazy dogs!", "  leading spaces and\nnew lines\n", "ünïcödé 你好 🙂", ""]
+
+
+def test_tokenize_and_detokenize_agree(pair):
+    ours, ref = pair
+    for t in TEXTS:
+        a, b = _post(ours, "/tokenize", {"content": t})["tokens"], _post(ref, "/tokenize", {"content": t})["tokens"]
+        assert a == b, t
+        assert _post(ours, "/tokenize", {"content": t, "add_special": True})["tokens"] == _post(ref, "/tokenize", {"content": t, "add_special": True})["tokens"]
+        if a:
+            assert _post(ours, "/detokenize", {"tokens": a})["content"] == _post(ref, "/detokenize", {"tokens": a})["content"]
+
+
+def _greedy(port, prompt, n=8, **extra):
+    d = _post(port, "/completion", {"prompt": prompt, "n_predict": n, "temperature": 0, "n_probs": 3, "cache_prompt": False, **extra})
+    return d, [p["id"] for p in d["completion_probabilities"]], [p["logprob"] for p in d["completion_probabilities"]]
+
+
+@pytest.mark.parametrize("prompt", ["hello there", "one two three four", "the cat sat on the"])
+def test_greedy_completion_and_probabilities_agree(pair, prompt):
+    """Same tokens and log-probabilities as the reference (fp32 vs ggml's fp16 KV: 1e-2); where the two pick different tokens the reference's
+    own top two candidates must be a near tie - a random-init model has many of those."""
+    ours, ref = pair
+    do, ido, lpo = _greedy(ours, prompt)
+    dr, idr, lpr = _greedy(ref, prompt)
+    assert do["tokens_evaluated"] == dr["tokens_evaluated"] and len(ido) == len(idr) == 8
+    for i, (a, b) in enumerate(zip(ido, idr)):
+        if a != b:
+            top = dr["completion_probabilities"][i]["top_logprobs"]
+            assert abs(top[0]["logprob"] - top[1]["logprob"]) < 2e-2, (i, ido, idr)
+            break
+        assert abs(lpo[i] - lpr[i]) < 1e-2
+        tr, to = dr["completion_probabilities"][i]["top_logprobs"], do["completion_probabilities"][i]["top_logprobs"]
+        assert [t["id"] for t in to][:1] == [t["id"] for t in tr][:1] and to[0]["token"] == tr[0]["token"]
+    else:
+        assert do["content"] == dr["content"]
+    assert i >= 3          # at least the first tokens line up on every prompt
+
+
+def test_logit_bias_grammar_and_stop_agree(pair):
+    ours, ref = pair
+    body = {"prompt": "hello", "n_predict": 5, "temperature": 0, "logit_bias": [[300, 100.0]], "cache_prompt": False}
+    a, b = _post(ours, "/completion", body), _post(ref, "/completion", body)
+    assert a["content"] == b["content"] != ""            # token 300 five times on both
+    g = {"prompt": "answer:", "n_predict": 12, "temperature": 0, "cache_prompt": False, "grammar": 'root ::= ("yes" | "no") " " [a-c] [a-c] [a-c]'}
+    a, b = _post(ours, "/completion", g), _post(ref, "/completion", g)
+    assert a["content"] == b["content"] and a["content"][:3] in ("yes", "no ")
+    js = {"prompt": "json:", "n_predict": 160, "temperature": 0, "cache_prompt": False,
+          "json_schema": {"type": "object", "properties": {"ok": {"type": "boolean"}, "n": {"enum": [1, 2, 3]}}, "required": ["ok", "n"]}}
+    a, b = _post(ours, "/completion", js), _post(ref, "/completion", js)
+    for d in (a, b):          # a random-init model may spend its budget on the white space a JSON grammar allows: complete -> valid, else a prefix
+        if d["stop_type"] in ("eos", "stop"):
+            v = json.loads(d["content"])
+            assert isinstance(v["ok"], bool) and v["n"] in (1, 2, 3)
+        else:
+            assert d["content"].lstrip().startswith("{")
+    assert a["stop_type"] == "stop" and json.loads(a["content"])["n"] in (1, 2, 3)       # ours bounds every repetition, so it always closes
+    # a stop string cuts both answers at the same place and is reported the same way
+    base = _post(ref, "/completion", {"prompt": "hello there", "n_predict": 8, "temperature": 0, "cache_prompt": False})["content"]
+    stop = base[3:5]
+    a = _post(ours, "/completion", {"prompt": "hello there", "n_predict": 8, "temperature": 0, "cache_prompt": False, "stop": [stop]})
+    b = _post(ref, "/completion", {"prompt": "hello there", "n_predict": 8, "temperature": 0, "cache_prompt": False, "stop": [stop]})
+    assert a["content"] == b["content"] == base[:base.index(stop)] and a["stop_type"] == "stop" and b["stop_type"] == "word"
+
+
+def test_openai_envelope_and_meta_routes_agree(pair):
+    ours, ref = pair
+    body = {"messages": [{"role": "user", "content": "hi"}], "max_tokens": 4, "temperature": 0}
+    a, b = _post(ours, "/v1/chat/completions", body), _post(ref, "/v1/chat/completions", body)
+    for d in (a, b):
+        assert d["object"] == "chat.completion" and d["choices"][0]["message"]["role"] == "assistant" and d["choices"][0]["finish_reason"] == "length"
+        assert set(d["usage"]) >= {"prompt_tokens", "completion_tokens", "total_tokens"} and d["usage"]["completion_tokens"] == 4
+    assert a["usage"]["prompt_tokens"] == b["usage"]["prompt_tokens"]            # the same template was rendered and tokenised
+    assert a["choices"][0]["message"]["content"] == b["choices"][0]["message"]["content"]
+    ta = _post(ours, "/apply-template", {"messages": body["messages"]})["prompt"]
+    assert ta == _post(ref, "/apply-template", {"messages": body["messages"]})["prompt"]
+    ma, mb = _get(ours, "/v1/models"), _get(ref, "/v1/models")
+    assert ma["object"] == mb["object"] == "list" and ma["data"][0]["object"] == mb["data"][0]["object"] == "model"
+    pa, pb = _get(ours, "/props"), _get(ref, "/props")
+    assert pa["total_slots"] == pb["total_slots"] == 2 and "default_generation_settings" in pa and "default_generation_settings" in pb
+    assert _get(ours, "/health")["status"] == _get(ref, "/health")["status"] == "ok"
