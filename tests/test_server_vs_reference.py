@@ -155,3 +155,33 @@ def test_openai_envelope_and_meta_routes_agree(pair):
     pa, pb = _get(ours, "/props"), _get(ref, "/props")
     assert pa["total_slots"] == pb["total_slots"] == 2 and "default_generation_settings" in pa and "default_generation_settings" in pb
     assert _get(ours, "/health")["status"] == _get(ref, "/health")["status"] == "ok"
+
+
+@pytest.mark.parametrize("pooling", ["mean", "last"])
+def test_embeddings_agree_with_reference_server(pair, tmp_models, tmp_path, pooling):
+    """`/embedding` (final-norm hidden states pooled over the sequence, L2-normalised) against `llama-server --embedding --pooling X`."""
+    ours, _ = pair
+    env = ref_build.cpu_env(str(tmp_path))
+    port = _free_port()
+    p = subprocess.Popen([ref_build.exe("llama-server"), "-m", tmp_models[("tiny", "F16")], "-ngl", "0", "-c", "256", "--host", "127.0.0.1", "--port", str(port), "-t", "2",
+                          "--no-warmup", "--embedding", "--pooling", pooling], env=env, stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL)
+    try:
+        for _ in range(200):
+            try:
+                _get(port, "/health")
+                break
+            except Exception:
+                time.sleep(0.1)
+        else:
+            pytest.skip("the reference server did not come up here")
+        for text in ["hello there world", "The quick brown fox jumps over the lazy dog"]:
+            r = _post(port, "/embedding", {"content": text})
+            rv = r[0]["embedding"] if isinstance(r, list) else r["embedding"]
+            rv = rv[0] if isinstance(rv[0], list) else rv
+            ov = _post(ours, "/embedding", {"content": text, "pooling": pooling})["embedding"]
+            assert len(rv) == len(ov)
+            dot = sum(a * b for a, b in zip(rv, ov))
+            assert dot > 0.9999 and abs(sum(a * a for a in ov) - 1.0) < 1e-3, (pooling, text, dot)
+    finally:
+        p.terminate()
+        p.wait()

@@ -281,3 +281,26 @@ def test_gguf_dump_hash_and_metadata_edit(tmp_models, tmp_path):
     assert "same tensor data" in _run("dlp_gguf.py", "hash", "-q", b, "--check", src)
     r = subprocess.run([sys.executable, os.path.join(REPO, "tools", "dlp_gguf.py"), "hash", "-q", b, "--check", tmp_models[("tiny", "F16")]], capture_output=True, text=True)
     assert r.returncode == 1 and "DIFFERENT" in r.stdout
+
+
+def test_perplexity_tool_matches_llama_perplexity(tmp_models, tmp_path):
+    """`dlp_perplexity.py` against the reference tool on the same file and text: same chunking (second half of every n_ctx window), same number."""
+    import re
+    sys.path.insert(0, REPO)
+    from baseline import reference as ref_build
+    why = ref_build.ensure(allow_build=False)
+    if why is not None or not ref_build.have("llama-perplexity"):
+        import pytest
+        pytest.skip(f"reference binaries unavailable: {why}")
+    rnd = np.random.default_rng(2)
+    words = ["alpha", "beta", "gamma", "delta", "the", "of", "and", "to", "in", "is"]
+    text = tmp_path / "t.txt"
+    text.write_text(" ".join(words[i] for i in rnd.integers(0, len(words), 1200)))
+    model = tmp_models[("tiny", "Q8_0")]
+    p = subprocess.run([ref_build.exe("llama-perplexity"), "-m", model, "-f", str(text), "-c", "64", "-b", "64", "--chunks", "3", "-ngl", "0", "-t", "4"],
+                       env=ref_build.cpu_env(str(tmp_path)), capture_output=True, text=True, timeout=600)
+    assert p.returncode == 0, p.stderr[-500:]
+    ref_ppl = float(re.search(r"Final estimate: PPL = ([0-9.]+)", p.stdout + p.stderr).group(1))
+    out = _run("dlp_perplexity.py", "-m", model, "-f", str(text), "-c", "64", "--chunks", "3", "--device", "cpu")
+    mine = float(re.search(r"Final estimate: PPL = ([0-9.]+)", out).group(1))
+    assert abs(mine - ref_ppl) / ref_ppl < 0.02, (mine, ref_ppl)

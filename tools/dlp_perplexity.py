@@ -36,19 +36,20 @@ def main(argv=None):
         ids = torch.randint(3, w.cfg.vocab_size, (a.ctx_size * a.chunks,), generator=g).tolist()
     nll, count = 0.0, 0
     n_chunks = min(a.chunks, len(ids) // a.ctx_size)
+    tok = Tokenizer(f.metadata)
+    half = a.ctx_size // 2
     for c in range(n_chunks):
-        chunk = ids[c * a.ctx_size:(c + 1) * a.ctx_size]
+        chunk = list(ids[c * a.ctx_size:(c + 1) * a.ctx_size])
+        if tok.add_bos:                 # every window starts with BOS, as the reference tool arranges it (perplexity.cpp:573-578)
+            chunk[0] = tok.bos_id
         sid = eng.alloc_seq()
-        half = a.ctx_size // 2
-        eng.prefill(sid, chunk[:half])
-        for i in range(half, a.ctx_size):            # teacher-forced decode over the second half
-            logits = eng.decode([sid], [chunk[i - 1]] if i > half else [chunk[half - 1]], sample=False)[0] if i > half else None
-            if logits is None:
-                eng.truncate_seq(sid, half - 1)
-                logits = eng.decode([sid], [chunk[half - 1]], sample=False)[0]
-            lp = torch.log_softmax(logits.float(), -1)[chunk[i]]
-            nll -= float(lp)
-            count += 1
+        logits = eng.prefill(sid, chunk, all_logits=True)          # one forward; logits of every position
+        lp = torch.log_softmax(logits.float(), -1)
+        # positions n_ctx/2 .. n_ctx-2 predict tokens n_ctx/2+1 .. n_ctx-1: the second half of the window, scored with at least half a
+        # window of context (perplexity.cpp:595-640 `first = n_ctx/2`)
+        tgt = torch.tensor(chunk[half + 1:], device=lp.device)
+        nll -= float(lp[half:a.ctx_size - 1].gather(1, tgt[:, None]).sum())
+        count += a.ctx_size - 1 - half
         eng.free_seq(sid)
         print(f"[{c + 1}/{n_chunks}] running PPL = {math.exp(nll / count):.4f}", flush=True)
     print(f"Final estimate: PPL = {math.exp(nll / max(1, count)):.4f} over {count} tokens")
