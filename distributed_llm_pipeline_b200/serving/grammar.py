@@ -338,61 +338,245 @@ array ::= "[" ws ( value ( ws "," ws value )* )? ws "]"
 '''
 
 
+def _digits_between(lo: str, hi: str) -> str:
+    """GBNF expression for the decimal strings of len(lo) == len(hi) digits between lo and hi inclusive (leading zeros allowed)."""
+    n = len(lo)
+    if n == 0:
+        return ""
+    if lo == "0" * n and hi == "9" * n:
+        return "[0-9]" if n == 1 else f"[0-9]{{{n}}}"
+    if lo[0] == hi[0]:
+        rest = _digits_between(lo[1:], hi[1:])
+        return f'"{lo[0]}"' + (f" {rest}" if rest else "")
+    alts = []
+    a, b = int(lo[0]), int(hi[0])
+    low_full, high_full = lo[1:] == "0" * (n - 1), hi[1:] == "9" * (n - 1)
+    if not low_full:                                     # the lowest leading digit with a constrained tail
+        alts.append(f'"{lo[0]}" {_digits_between(lo[1:], "9" * (n - 1))}')
+        a += 1
+    if not high_full:
+        b -= 1
+    if a <= b:                                           # leading digits whose tail is free
+        head = f'"{a}"' if a == b else f"[{a}-{b}]"
+        alts.append(head + ("" if n == 1 else " [0-9]" if n == 2 else f" [0-9]{{{n - 1}}}"))
+    if not high_full:
+        alts.append(f'"{hi[0]}" {_digits_between("0" * (n - 1), hi[1:])}')
+    return "( " + " | ".join(alts) + " )" if len(alts) > 1 else alts[0]
+
+
+def _nonneg_range(lo: int, hi: int | None) -> list[str]:
+    """Alternatives covering the integers lo..hi (hi None = unbounded, up to 16 digits) written without leading zeros."""
+    alts = []
+    top = hi if hi is not None else 10 ** 16 - 1
+    for n in range(len(str(lo)), len(str(top)) + 1):
+        a = max(lo, 0 if n == 1 else 10 ** (n - 1))
+        b = min(top, 10 ** n - 1)
+        if a <= b:
+            alts.append(_digits_between(str(a).zfill(n), str(b).zfill(n)))
+    return alts
+
+
+def int_range_gbnf(lo: int | None, hi: int | None) -> str:
+    """GBNF expression for the integers in [lo, hi] (either bound may be None)."""
+    if lo is None and hi is None:
+        return "integer"
+    alts = []
+    if lo is None or lo < 0:                              # negative part: "-" followed by a magnitude in [max(1, -hi), -lo]
+        mag_lo = 1 if (hi is None or hi >= 0) else -hi
+        mag = _nonneg_range(mag_lo, None if lo is None else -lo)
+        if mag:
+            alts.append('"-" ( ' + " | ".join(mag) + " )")
+    if hi is None or hi >= 0:
+        alts += _nonneg_range(max(lo or 0, 0) if lo is not None else 0, hi)
+    return "( " + " | ".join(alts) + " )"
+
+
+_Q = '"\\""'      # the GBNF literal for one double-quote character
+_FORMATS = {
+    "date": f"{_Q} date {_Q}", "time": f"{_Q} time {_Q}", "date-time": f'{_Q} date "T" time {_Q}',
+    "uuid": f'{_Q} hex{{8}} "-" hex{{4}} "-" hex{{4}} "-" hex{{4}} "-" hex{{12}} {_Q}',
+}
+_FORMAT_PRIMS = r'''
+date ::= [0-9]{4} "-" ( "0" [1-9] | "1" [0-2] ) "-" ( "0" [1-9] | [1-2] [0-9] | "3" [0-1] )
+time ::= ( [01] [0-9] | "2" [0-3] ) ":" [0-5] [0-9] ":" [0-5] [0-9] ( "." [0-9]{3} )? ( "Z" | ( "+" | "-" ) ( [01] [0-9] | "2" [0-3] ) ":" [0-5] [0-9] )
+hex ::= [0-9a-fA-F]
+char ::= [^"\\\x00-\x1f] | "\\" ( ["\\/bfnrt] | "u" [0-9a-fA-F]{4} )
+'''
+
+
 def json_schema_to_gbnf(schema: dict | None) -> str:
-    """GBNF for JSON documents matching `schema` (None / {} = any JSON value)."""
-    rules: list[str] = []
-    counter = [0]
+    """GBNF for JSON documents matching `schema` (None / {} = any JSON value).
+
+    Covers what the reference's converter does for the schemas LLM tooling sends (`common/json-schema-to-grammar.cpp`): `$ref` into
+    `$defs` / `definitions`, `allOf` (objects merged), `anyOf` / `oneOf`, `const` / `enum`, type lists, objects with required and
+    optional properties in declaration order and `additionalProperties`, arrays with `items` / `prefixItems` / `minItems` / `maxItems`,
+    strings with `minLength` / `maxLength` and the `date`, `time`, `date-time`, `uuid` formats, integers with `minimum` / `maximum` /
+    `exclusiveMinimum` / `exclusiveMaximum`.  `pattern` is not translated (the string stays unconstrained).  Every repetition in the
+    generated grammar is bounded, so a constrained generation always terminates."""
+    root_schema = schema or {}
+    rules: dict[str, str] = {}
+    uses_format = [False]
 
     def lit(v) -> str:
         return '"' + json.dumps(v).replace("\\", "\\\\").replace('"', '\\"') + '"'
 
+    def rule_name(base: str) -> str:
+        base = "".join(c if (c.isalnum() or c == "-") else "-" for c in base) or "r"
+        n, i = base, 1
+        while n in rules:
+            i += 1
+            n = f"{base}{i}"
+        rules[n] = ""
+        return n
+
+    def resolve(sc: dict) -> dict:
+        seen = 0
+        while isinstance(sc, dict) and "$ref" in sc and seen < 32:
+            ref = sc["$ref"]
+            if not ref.startswith("#/"):
+                raise GrammarError(f"unsupported $ref {ref!r} (only references into this schema)")
+            node = root_schema
+            for part in ref[2:].split("/"):
+                node = node[part.replace("~1", "/").replace("~0", "~")]
+            sc, seen = {**node, **{k: v for k, v in sc.items() if k != "$ref"}}, seen + 1
+        return sc
+
+    def merge_all_of(sc: dict) -> dict:
+        out = {k: v for k, v in sc.items() if k != "allOf"}
+        for sub in sc["allOf"]:
+            sub = resolve(sub)
+            if "allOf" in sub:
+                sub = merge_all_of(sub)
+            for k, v in sub.items():
+                if k == "properties":
+                    out["properties"] = {**out.get("properties", {}), **v}
+                elif k == "required":
+                    out["required"] = list(dict.fromkeys(list(out.get("required", [])) + list(v)))
+                else:
+                    out.setdefault(k, v)
+        return out
+
+    def obj(sc: dict, name: str) -> str:
+        props = sc.get("properties", {})
+        req = set(sc.get("required", []))
+        extra = sc.get("additionalProperties", False if props else True)
+        kvs = []
+        for k in props:
+            sub = visit(props[k], f"{name}-{k}")
+            kvs.append((k in req, f'{lit(k)} ws ":" ws {sub}'))
+        extra_kv = None
+        if extra is not False:
+            ev = visit(extra if isinstance(extra, dict) else {}, f"{name}-extra")
+            extra_kv = f'string ws ":" ws {ev}'
+        n = len(kvs)
+        memo: dict[tuple[int, bool], str] = {}
+
+        def rest(i: int, first: bool) -> str:
+            """Rule for the properties from index i on; `first`: nothing has been written yet, so no comma goes in front."""
+            key = (i, first)
+            if key in memo:
+                return memo[key]
+            sep = "" if first else 'ws "," ws '
+            if i == n:
+                if extra_kv is None:
+                    memo[key] = ""
+                    return ""
+                rn = rule_name(f"{name}-more")
+                rules[rn] = f'( {sep}{extra_kv} ( ws "," ws {extra_kv} ){{0,15}} )?'
+                memo[key] = rn
+                return rn
+            required, kv = kvs[i]
+            after = rest(i + 1, False)
+            taken = f"{sep}{kv}" + (f" {after}" if after else "")
+            if required:
+                body = taken
+            else:
+                skipped = rest(i + 1, first)
+                body = f"( {taken} | {skipped} )" if skipped else f"( {taken} )?"
+            rn = rule_name(f"{name}-p{i}{'a' if first else 'b'}")
+            rules[rn] = body
+            memo[key] = rn
+            return rn
+        inner = rest(0, True)
+        rn = rule_name(name)
+        rules[rn] = '"{" ws ' + (f"{inner} " if inner else "") + 'ws "}"'
+        return rn
+
+    def arr(sc: dict, name: str) -> str:
+        rn = rule_name(name)
+        if "prefixItems" in sc:
+            items = [visit(x, f"{name}-t{i}") for i, x in enumerate(sc["prefixItems"])]
+            rules[rn] = '"[" ws ' + ' ws "," ws '.join(items) + ' ws "]"'
+            return rn
+        item = visit(sc.get("items", {}), f"{name}-item")
+        lo, hi = int(sc.get("minItems", 0)), sc.get("maxItems")
+        hi = int(hi) if hi is not None else max(lo, 1) + 31
+        if hi <= 0:
+            rules[rn] = '"[" ws "]"'
+            return rn
+        more = f'( ws "," ws {item} ){{{max(0, lo - 1)},{hi - 1}}}'
+        inner = f"{item} {more}"
+        rules[rn] = '"[" ws ' + (f"( {inner} )?" if lo == 0 else inner) + ' ws "]"'
+        return rn
+
     def visit(sc, name: str) -> str:
-        if not sc:
+        if sc is True or sc is None or sc == {}:
             return "value"
+        sc = resolve(sc)
+        if "allOf" in sc:
+            sc = merge_all_of(sc)
         if "const" in sc:
             return lit(sc["const"])
         if "enum" in sc:
-            rules.append(f"{name} ::= " + " | ".join(lit(v) for v in sc["enum"]))
-            return name
+            rn = rule_name(name)
+            rules[rn] = " | ".join(lit(v) for v in sc["enum"])
+            return rn
         if "anyOf" in sc or "oneOf" in sc:
             alts = sc.get("anyOf") or sc.get("oneOf")
-            parts = []
-            for i, sub in enumerate(alts):
-                parts.append(visit(sub, f"{name}-{i}"))
-            rules.append(f"{name} ::= " + " | ".join(parts))
-            return name
+            rn = rule_name(name)
+            rules[rn] = " | ".join(visit(sub, f"{name}-{i}") for i, sub in enumerate(alts))
+            return rn
         t = sc.get("type")
         if isinstance(t, list):
-            rules.append(f"{name} ::= " + " | ".join(visit({**sc, "type": x}, f"{name}-{x}") for x in t))
-            return name
-        if t == "object" and "properties" in sc:
-            props = sc["properties"]
-            req = sc.get("required", list(props))
-            parts = []
-            for k in props:                      # emitted in declaration order; optional ones may be skipped
-                counter[0] += 1
-                sub = visit(props[k], f"{name}-{k}".replace("_", "-"))
-                parts.append((k in req, f'{lit(k)} ws ":" ws {sub}'))
-            body, first = "", True
-            for required, p in parts:
-                sep = "" if first else 'ws "," ws '
-                if required:
-                    body += f" {sep}{p}"
-                    first = False
-                else:
-                    body += f" ( {sep}{p} )?" if not first else f" ( {p} ws \",\" ws )?"
-            rules.append(f'{name} ::= "{{" ws{body} ws "}}"')
-            return name
-        if t == "array" and "items" in sc:
-            item = visit(sc["items"], f"{name}-item")
-            lo, hi = sc.get("minItems", 0), sc.get("maxItems")
-            rep = f'( ws "," ws {item} )' + ("*" if hi is None else f"{{0,{max(0, hi - 1)}}}")
-            inner = f"{item} {rep}"
-            rules.append(f'{name} ::= "[" ws ' + (f"( {inner} )?" if lo == 0 else inner) + ' ws "]"')
-            return name
-        if t in ("string", "integer", "number", "boolean", "null", "object", "array"):
+            rn = rule_name(name)
+            rules[rn] = " | ".join(visit({**sc, "type": x}, f"{name}-{x}") for x in t)
+            return rn
+        if t == "object" or (t is None and ("properties" in sc or "additionalProperties" in sc)):
+            if "properties" not in sc and sc.get("additionalProperties", True) is True:
+                return "object"
+            return obj(sc, name)
+        if t == "array" or (t is None and ("items" in sc or "prefixItems" in sc)):
+            if "items" not in sc and "prefixItems" not in sc and "minItems" not in sc and "maxItems" not in sc:
+                return "array"
+            return arr(sc, name)
+        if t == "string":
+            if sc.get("format") in _FORMATS:
+                uses_format[0] = True
+                rn = rule_name(name)
+                rules[rn] = _FORMATS[sc["format"]]
+                return rn
+            if "minLength" in sc or "maxLength" in sc:
+                uses_format[0] = True
+                lo, hi = int(sc.get("minLength", 0)), sc.get("maxLength")
+                rn = rule_name(name)
+                rules[rn] = '"\\"" char' + (f"{{{lo},{int(hi)}}}" if hi is not None else f"{{{lo},{lo + 256}}}") + ' "\\""'
+                return rn
+            return "string"
+        if t == "integer":
+            lo, hi = sc.get("minimum"), sc.get("maximum")
+            if "exclusiveMinimum" in sc:
+                lo = int(sc["exclusiveMinimum"]) + 1
+            if "exclusiveMaximum" in sc:
+                hi = int(sc["exclusiveMaximum"]) - 1
+            if lo is None and hi is None:
+                return "integer"
+            rn = rule_name(name)
+            rules[rn] = int_range_gbnf(None if lo is None else int(lo), None if hi is None else int(hi))
+            return rn
+        if t in ("number", "boolean", "null"):
             return t
         return "value"
 
-    root = visit(schema or {}, "root-v")
-    return f"root ::= {root}\n" + "\n".join(rules) + "\n" + _JSON_PRIMS
+    root = visit(root_schema, "root-v")
+    body = "\n".join(f"{k} ::= {v}" for k, v in rules.items())
+    return f"root ::= {root}\n{body}\n" + _JSON_PRIMS + (_FORMAT_PRIMS if uses_format[0] else "")
