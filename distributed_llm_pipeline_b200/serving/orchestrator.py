@@ -397,6 +397,11 @@ class Orchestrator:
                               dynatemp_exponent=float(d.get("dynatemp_exponent", 1.0)), xtc_probability=float(d.get("xtc_probability", 0.0)),
                               xtc_threshold=float(d.get("xtc_threshold", 0.1)), mirostat=int(d.get("mirostat", 0)),
                               mirostat_tau=float(d.get("mirostat_tau", 5.0)), mirostat_eta=float(d.get("mirostat_eta", 0.1)),
+                              dry_multiplier=float(d.get("dry_multiplier", 0.0)), dry_base=float(d.get("dry_base", 1.75)),
+                              dry_allowed_length=int(d.get("dry_allowed_length", 2)), dry_penalty_last_n=int(d.get("dry_penalty_last_n", -1)),
+                              dry_breakers=tuple(t for b in (d.get("dry_sequence_breakers") if d.get("dry_sequence_breakers") is not None else ["\n", ":", "\"", "*"])
+                                                 for t in self.sched.tok.encode(str(b), add_bos=False)[-1:]),
+                              repeat_last_n=int(d.get("repeat_last_n", 64)),
                               logit_bias={int(k): float(v) for k, v in (d.get("logit_bias") or {}).items()} if isinstance(d.get("logit_bias"), dict)
                               else {int(k): float(v) for k, v in (d.get("logit_bias") or [])},
                               temperature=float(d.get("temperature", 0.8)), top_k=int(d.get("top_k", 40)), top_p=float(d.get("top_p", 0.95)),

