@@ -206,3 +206,35 @@ def test_deterministic_sampler_stages_agree(pair, extra):
         agree += 1
     assert agree >= 6 or agree == len(idr), (ido, idr)
     assert idr != base or "logit_bias" in extra          # the stage under test actually changed the reference's output
+
+
+@pytest.mark.parametrize("params", [{"top_k": 10, "top_p": 1.0, "min_p": 0.0, "temperature": 1.0}, {"top_k": 0, "top_p": 0.3, "min_p": 0.0, "temperature": 0.7},
+                                    {"top_k": 0, "top_p": 1.0, "min_p": 0.4, "temperature": 1.5}, {"top_k": 40, "top_p": 0.9, "min_p": 0.05, "temperature": 0.8},
+                                    {"top_k": 0, "top_p": 1.0, "min_p": 0.0, "typical_p": 0.2, "temperature": 1.0}],
+                         ids=["top-k", "top-p", "min-p", "default-chain", "typical"])
+def test_truncation_samplers_leave_the_same_candidates(pair, params):
+    """top-k / typical / top-p / min-p / temperature: the reference reports the distribution AFTER its sampler chain
+    (`post_sampling_probs`); the same chain applied here (`filter_candidates` + temperature) to the same logits - taken from the
+    reference's own full-vocabulary probabilities - must keep the same tokens with the same probabilities."""
+    import math
+
+    import torch
+
+    from distributed_llm_pipeline_b200.serving.sampler import filter_candidates
+    _, ref = pair
+    prompt = "the quick brown fox"
+    body = {"prompt": prompt, "n_predict": 2, "n_probs": 512, "seed": 1, "cache_prompt": False,
+            "samplers": ["top_k", "typ_p", "top_p", "min_p", "temperature"], "typical_p": 1.0, **params}
+    # the same request twice: once for the distribution in front of the chain, once for the one behind it
+    top = _post(ref, "/completion", body)["completion_probabilities"][0]["top_logprobs"]
+    assert len(top) == 512
+    logits = torch.full((512,), -1e9)
+    for t in top:
+        logits[t["id"]] = t["logprob"]
+    post = _post(ref, "/completion", {**body, "post_sampling_probs": True})["completion_probabilities"][0]["top_probs"]
+    theirs = {t["id"]: t["prob"] for t in post if t["prob"] > 0}
+    vals, ids = filter_candidates(logits, params["top_k"], params["top_p"], params["min_p"], params.get("typical_p", 1.0))
+    probs = torch.softmax(vals / params["temperature"], -1)
+    mine = {int(i): float(p) for i, p in zip(ids, probs)}
+    assert set(mine) == set(theirs), (sorted(set(mine) ^ set(theirs)), len(mine), len(theirs))
+    assert all(math.isclose(mine[i], theirs[i], rel_tol=2e-3, abs_tol=1e-5) for i in mine)
