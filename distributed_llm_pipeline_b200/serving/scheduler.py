@@ -446,7 +446,8 @@ class Scheduler:
         elif s.n_past + 1 >= self.eng.n_ctx:
             if self.context_shift and hasattr(self.eng, "shift_seq"):
                 # keep the first n_keep tokens, drop half of the rest (server-context.cpp:1944-2003)
-                n_keep = min(req.n_keep if req.n_keep >= 0 else len(req.prompt_ids), self.eng.n_ctx - 4)
+                n_keep = (req.n_keep if req.n_keep >= 0 else len(req.prompt_ids)) + (1 if self.tok.add_bos else 0)     # n_keep does not count BOS
+                n_keep = min(n_keep, self.eng.n_ctx - 4)
                 n_discard = (s.n_past - n_keep) // 2
                 self.eng.shift_seq(s.sid, n_keep, n_discard)
                 del s.cache_tokens[n_keep:n_keep + n_discard]

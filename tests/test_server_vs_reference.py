@@ -238,3 +238,108 @@ def test_truncation_samplers_leave_the_same_candidates(pair, params):
     mine = {int(i): float(p) for i, p in zip(ids, probs)}
     assert set(mine) == set(theirs), (sorted(set(mine) ^ set(theirs)), len(mine), len(theirs))
     assert all(math.isclose(mine[i], theirs[i], rel_tol=2e-3, abs_tol=1e-5) for i in mine)
+
+
+def test_infill_prompt_is_built_the_same_way(tmp_models, tmp_path):
+    """`/infill`: <FIM_PRE> prefix <FIM_SUF> suffix <FIM_MID> behind BOS (server-common.cpp `format_infill`); both servers report how many
+    tokens they evaluated and echo the prompt, and greedy decoding from it gives the same text."""
+    import numpy as np
+
+    from distributed_llm_pipeline_b200.gguf import GGUFWriter, open_gguf
+    from distributed_llm_pipeline_b200.gguf.constants import ValueType
+    why = ref_build.ensure(allow_build=False)
+    if why is not None or not ref_build.have("llama-server"):
+        pytest.skip(f"reference binaries unavailable: {why}")
+    f = open_gguf(tmp_models[("tiny", "F16")])
+    model = str(tmp_path / "fim.gguf")
+    w = GGUFWriter(model)
+    for k, v in f.metadata.items():
+        w.add(k, v, f.files[0].metadata_types[k]) if not isinstance(v, (list, np.ndarray)) else w.add(k, v)
+    for key, tid in (("pre", 500), ("suf", 501), ("mid", 502)):
+        w.add(f"tokenizer.ggml.fim_{key}_token_id", tid, ValueType.UINT32)
+    for n, t in f.tensors.items():
+        w.add_tensor(n, t.shape, t.ggml_type, lambda n=n: np.ascontiguousarray(f.raw(n)).reshape(-1))
+    w.write()
+    env = ref_build.cpu_env(str(tmp_path))
+    rp = _free_port()
+    proc = subprocess.Popen([ref_build.exe("llama-server"), "-m", model, "-ngl", "0", "-c", "512", "--host", "127.0.0.1", "--port", str(rp), "-t", "2", "--no-warmup"],
+                            env=env, stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL)
+    sched, info, logs = build_service(model, device="cpu", n_ctx=512, n_slots=1, n_batch=64)
+    sched.start()
+    try:
+        for _ in range(200):
+            try:
+                _get(rp, "/health")
+                break
+            except Exception:
+                time.sleep(0.1)
+        else:
+            pytest.skip("the reference server did not come up here")
+        orch = Orchestrator(sched, info, n_predict=8, startup_logs=logs)
+        op = _free_port()
+        loop = asyncio.new_event_loop()
+        threading.Thread(target=lambda: loop.run_until_complete(orch.serve("127.0.0.1", op)), daemon=True).start()
+        time.sleep(0.5)
+        body = {"input_prefix": "def add(a, b):\n    return ", "input_suffix": "\n\nprint(add(1, 2))\n", "n_predict": 6, "temperature": 0, "cache_prompt": False,
+                "samplers": ["top_k"], "top_k": 1}
+        a, b = _post(op, "/infill", body), _post(rp, "/infill", body)
+        assert a["tokens_evaluated"] == b["tokens_evaluated"] > 20
+        assert a["content"] == b["content"]
+    finally:
+        sched.stop()
+        proc.terminate()
+        proc.wait()
+
+
+def test_context_shift_keeps_generating_like_the_reference(tmp_models, tmp_path):
+    """Generation past the end of the context with `--context-shift`: both servers keep `n_keep` tokens, drop half of the rest and re-rotate
+    the cached keys (server-context.cpp:1944-2003, llama-kv-cache.cpp K-shift); the greedy continuation after the shift must be the same."""
+    why = ref_build.ensure(allow_build=False)
+    if why is not None or not ref_build.have("llama-server"):
+        pytest.skip(f"reference binaries unavailable: {why}")
+    model = tmp_models[("tiny", "F16")]
+    env = ref_build.cpu_env(str(tmp_path))
+    rp = _free_port()
+    proc = subprocess.Popen([ref_build.exe("llama-server"), "-m", model, "-ngl", "0", "-c", "256", "-np", "1", "--host", "127.0.0.1", "--port", str(rp), "-t", "2", "--no-warmup",
+                             "--context-shift"], env=env, stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL)
+    sched, info, logs = build_service(model, device="cpu", n_ctx=256, n_slots=1, n_batch=64)        # 256 is the smallest window the reference makes
+    sched.context_shift = True
+    sched.start()
+    try:
+        for _ in range(200):
+            try:
+                _get(rp, "/health")
+                break
+            except Exception:
+                time.sleep(0.1)
+        else:
+            pytest.skip("the reference server did not come up here")
+        orch = Orchestrator(sched, info, n_predict=8, startup_logs=logs)
+        op = _free_port()
+        loop = asyncio.new_event_loop()
+        threading.Thread(target=lambda: loop.run_until_complete(orch.serve("127.0.0.1", op)), daemon=True).start()
+        time.sleep(0.5)
+        # a +100 bias pins the generated token on both servers, so the two caches hold the same text all the way; what is compared is the
+        # model's own (pre-bias) distribution at every step - before, at and after the shift
+        body = {"prompt": "one two three four five six seven", "n_predict": 260, "temperature": 0, "cache_prompt": False, "n_keep": 4, "ignore_eos": True,
+                "n_probs": 3, "logit_bias": [[300, 100.0]]}
+        a, b = _post(op, "/completion", body), _post(rp, "/completion", body)
+        pa, pb = a["completion_probabilities"], b["completion_probabilities"]
+        assert len(pa) == len(pb) == 260 and a["tokens_evaluated"] == b["tokens_evaluated"]
+        assert all(x["id"] == y["id"] == 300 for x, y in zip(pa, pb))
+        first_shift = 256 - a["tokens_evaluated"]
+        assert 0 < first_shift < 240
+        worst = 0.0
+        for i, (x, y) in enumerate(zip(pa, pb)):
+            tx, ty = x["top_logprobs"][0], y["top_logprobs"][0]
+            gap = abs(y["top_logprobs"][0]["logprob"] - y["top_logprobs"][1]["logprob"])
+            assert tx["id"] == ty["id"] or gap < 2e-2, (i, first_shift, tx, ty)
+            worst = max(worst, abs(x["logprob"] - y["logprob"]))
+        assert worst < 2e-2, (worst, first_shift)
+        # and the shift is visible at all: the forced token's log-probability moves when half of the context disappears
+        jump = abs(pb[first_shift + 1]["logprob"] - pb[first_shift - 2]["logprob"])
+        assert jump > 1e-3, jump
+    finally:
+        sched.stop()
+        proc.terminate()
+        proc.wait()
