@@ -186,7 +186,7 @@ class ReferenceModel:
             g = self.mm(x, p + "ffn_gate.weight")
             u = self.mm(x, p + "ffn_up.weight")
             return self.mm(torch.nn.functional.silu(g) * u, p + "ffn_down.weight")
-        logits = x @ w[p + "ffn_gate_inp.weight"].T
+        logits = self.mm(x, p + "ffn_gate_inp.weight")
         probs = torch.softmax(logits, dim=-1)
         topw, topi = probs.topk(c.n_expert_used, dim=-1)
         if c.moe_norm_topk:

@@ -1,0 +1,120 @@
+"""Tool interoperability with the reference's own command-line tools (CPU builds of `llama-quantize`, `llama-imatrix`, `llama-gguf-split`,
+`llama-export-lora`; looked for in `baseline/_ref/bin_cpu`, `$DLP_REF_CPU_TOOLS` or `/tmp/refcpu/bin` - build them with
+`tools/build_reference.sh cpu-tools`; the tests skip where they are absent).  Files move in both directions: what one side writes the other
+side reads, and the numbers agree."""
+import os
+import subprocess
+import sys
+
+import numpy as np
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tools"))
+
+from distributed_llm_pipeline_b200.gguf import GGMLType, open_gguf  # noqa: E402
+
+
+def tool(name: str) -> str:
+    for d in (os.environ.get("DLP_REF_CPU_TOOLS"), os.path.join(ROOT, "baseline", "_ref", "bin_cpu"), "/tmp/refcpu/bin"):
+        if d and os.path.exists(os.path.join(d, name)):
+            return os.path.join(d, name)
+    pytest.skip(f"reference tool {name} is not built here")
+
+
+def run(cmd, **kw):
+    p = subprocess.run(cmd, capture_output=True, text=True, timeout=600, **kw)
+    assert p.returncode == 0, (cmd, (p.stderr or p.stdout)[-800:])
+    return p.stdout + p.stderr
+
+
+def ours(script, *args):
+    return run([sys.executable, os.path.join(ROOT, "tools", script), *args], env=dict(os.environ, CUDA_VISIBLE_DEVICES=""))
+
+
+@pytest.mark.parametrize("ftype", ["Q4_K_M", "Q5_K_M", "Q8_0", "Q6_K", "Q3_K", "IQ4_NL"])
+def test_quantizer_picks_the_same_types_and_comparable_error(tmp_models, tmp_path, ftype):
+    """Per-tensor storage types equal to `llama-quantize`'s for the same file type (the Q4_K_M / Q5_K_M mix rules included), RMS error of the
+    own encoders within a few percent of the reference's, Q8_0 bytes equal up to rounding of exact ties."""
+    src = tmp_models[("tiny", "F16")]
+    ref_out, our_out = str(tmp_path / "ref.gguf"), str(tmp_path / "ours.gguf")
+    run([tool("llama-quantize"), src, ref_out, {"Q3_K": "Q3_K_S"}.get(ftype, ftype)])
+    ours("dlp_quantize.py", src, our_out, ftype)
+    s, r, o = open_gguf(src), open_gguf(ref_out), open_gguf(our_out)
+    assert set(r.tensors) == set(o.tensors)
+    for n in s.tensors:
+        tr, to = GGMLType(r.tensors[n].ggml_type), GGMLType(o.tensors[n].ggml_type)
+        assert tr == to, (n, tr.name, to.name)
+        if tr in (GGMLType.F32, GGMLType.F16):
+            continue
+        a = s.array(n)
+        er, eo = float(((r.array(n) - a) ** 2).mean() ** 0.5), float(((o.array(n) - a) ** 2).mean() ** 0.5)
+        assert eo < er * (1.06 if tr in (GGMLType.Q4_K, GGMLType.Q5_K, GGMLType.Q6_K, GGMLType.Q8_0) else 1.6), (n, tr.name, er, eo)
+        if tr == GGMLType.Q8_0:      # same scales; a few values that sit exactly between two steps may round the other way
+            assert float((np.asarray(r.raw(n)) != np.asarray(o.raw(n))).mean()) < 2e-3, n
+
+
+def test_imatrix_files_travel_both_ways(tmp_models, tmp_path):
+    import dlp_imatrix
+    model = tmp_models[("tiny-moe", "F16")]
+    text = tmp_path / "calib.txt"
+    rnd = np.random.default_rng(0)
+    words = ["alpha", "beta", "gamma", "delta", "the", "of", "and", "to", "in", "is", "it", "pipe", "line", "gpu", "token", "model"]
+    text.write_text(" ".join(words[i] for i in rnd.integers(0, len(words), 1500)))
+    ref_im, our_im = str(tmp_path / "ref_im.gguf"), str(tmp_path / "our_im.gguf")
+    run([tool("llama-imatrix"), "-m", model, "-f", str(text), "-o", ref_im, "-c", "64", "--chunks", "4", "-t", "4"])
+    ours("dlp_imatrix.py", "-m", model, "-f", str(text), "-o", our_im, "-c", "64", "--chunks", "4")
+    fr, fo = open_gguf(ref_im), open_gguf(our_im)
+    assert {k: fr.metadata[k] for k in ("general.type", "imatrix.chunk_count", "imatrix.chunk_size")} == {k: fo.metadata[k] for k in ("general.type", "imatrix.chunk_count", "imatrix.chunk_size")}
+    assert set(fr.tensors) == set(fo.tensors)                       # the same matrices were measured, routers included
+    for n in fr.tensors:
+        a, b = np.asarray(fr.array(n)).reshape(-1), np.asarray(fo.array(n)).reshape(-1)
+        if "_exps." in n or "gate_inp" in n:                       # routed experts: a near-tied routing decision may move a token between experts
+            assert np.abs(a - b).max() <= 0.05 * np.abs(a).max() + 4, n
+        else:
+            assert np.abs(a - b).max() <= 2e-3 * np.abs(a).max(), n
+    # each quantizer accepts the other side's file
+    run([tool("llama-quantize"), "--imatrix", our_im, model, str(tmp_path / "q_ref.gguf"), "Q4_K_M"])
+    log = ours("dlp_quantize.py", model, str(tmp_path / "q_ours.gguf"), "Q4_K_M", "--imatrix", ref_im)
+    assert "tensors weighted" in log
+    assert set(dlp_imatrix.load(ref_im)) == set(dlp_imatrix.load(our_im))
+
+
+def test_split_files_travel_both_ways(tmp_models, tmp_path):
+    import dlp_gguf
+    src = tmp_models[("tiny", "Q8_0")]
+    _, whole = dlp_gguf.tensor_hashes(src)
+    # ours splits, the reference merges
+    ours("dlp_gguf_split.py", "--split", "--split-max-tensors", "7", src, str(tmp_path / "ours"))
+    shards = sorted(p for p in os.listdir(tmp_path) if p.startswith("ours-"))
+    assert len(shards) >= 3
+    run([tool("llama-gguf-split"), "--merge", str(tmp_path / shards[0]), str(tmp_path / "merged_by_ref.gguf")])
+    assert dlp_gguf.tensor_hashes(str(tmp_path / "merged_by_ref.gguf"))[1] == whole
+    # the reference splits, ours reads the set and merges it
+    run([tool("llama-gguf-split"), "--split", "--split-max-tensors", "7", src, str(tmp_path / "ref")])
+    first = sorted(p for p in os.listdir(tmp_path) if p.startswith("ref-"))[0]
+    f = open_gguf(str(tmp_path / first))
+    assert set(f.tensors) == set(open_gguf(src).tensors)
+    ours("dlp_gguf_split.py", "--merge", str(tmp_path / first), str(tmp_path / "merged_by_ours.gguf"))
+    assert dlp_gguf.tensor_hashes(str(tmp_path / "merged_by_ours.gguf"))[1] == whole
+
+
+def test_export_lora_merges_like_the_reference(tmp_models, tmp_path):
+    from distributed_llm_pipeline_b200.models.weights import write_lora_gguf
+    base = tmp_models[("tiny", "F16")]
+    s = open_gguf(base)
+    rng = np.random.default_rng(1)
+    deltas = {}
+    for n in ("blk.0.attn_q.weight", "blk.1.ffn_down.weight", "blk.1.attn_v.weight"):
+        shape = s.tensors[n].shape
+        deltas[n] = ((rng.standard_normal((4, shape[1])) * 0.05).astype(np.float32), (rng.standard_normal((shape[0], 4)) * 0.05).astype(np.float32))
+    ad = write_lora_gguf(str(tmp_path / "ad.gguf"), deltas, 8.0, "llama")
+    run([tool("llama-export-lora"), "-m", base, "--lora", ad, "-o", str(tmp_path / "ref_merged.gguf")])
+    ours("dlp_export_lora.py", "-m", base, "--lora", ad, "-o", str(tmp_path / "our_merged.gguf"))
+    r, o = open_gguf(str(tmp_path / "ref_merged.gguf")), open_gguf(str(tmp_path / "our_merged.gguf"))
+    for n in s.tensors:
+        a, b = r.array(n), o.array(n)
+        assert np.abs(a - b).max() < 2e-3, n
+        if n in deltas:
+            assert np.abs(a - s.array(n)).max() > 1e-2           # the adapter really was merged

@@ -21,12 +21,15 @@ from distributed_llm_pipeline_b200.gguf.constants import ValueType  # noqa: E402
 
 
 class Collector:
-    def __init__(self, model):
+    def __init__(self, model, process_output: bool = False):
         self.model = model
+        self.process_output = process_output     # the output matrix is only measured on request (imatrix.cpp `--process-output`)
         self.sum2: dict[str, np.ndarray] = {}
         self.counts: dict[str, np.ndarray] = {}
 
     def __call__(self, name: str, x: torch.Tensor, expert):
+        if not name.startswith("blk.") and not self.process_output:
+            return
         w = self.model.w[name]
         n_mat = w.shape[0] if w.dim() == 3 else 1
         K = w.shape[-1]
@@ -39,16 +42,22 @@ class Collector:
         self.counts[name][e, 0] += x2.shape[0]
 
 
-def collect(model_path: str, token_ids: list[int], n_ctx: int, n_chunks: int, log=print):
+def collect(model_path: str, token_ids: list[int], n_ctx: int, n_chunks: int, log=print, process_output: bool = False):
+    from distributed_llm_pipeline_b200.gguf import open_gguf as _open
     from distributed_llm_pipeline_b200.models.reference import ReferenceModel
     m = ReferenceModel.from_gguf(model_path)
-    col = Collector(m)
+    md = _open(model_path).metadata
+    bos = int(md.get("tokenizer.ggml.bos_token_id", 1)) if md.get("tokenizer.ggml.add_bos_token", md.get("tokenizer.ggml.model", "llama") == "llama") else None
+    col = Collector(m, process_output)
     m.observer = col
     n_chunks = min(n_chunks if n_chunks > 0 else 1 << 30, len(token_ids) // n_ctx)
     if n_chunks < 1:
         raise SystemExit(f"the calibration text has {len(token_ids)} tokens: fewer than one chunk of {n_ctx}")
     for c in range(n_chunks):
-        m.forward(token_ids[c * n_ctx:(c + 1) * n_ctx], m.new_cache(n_ctx))
+        chunk = list(token_ids[c * n_ctx:(c + 1) * n_ctx])
+        if bos is not None:
+            chunk[0] = bos           # every window starts with BOS, as the reference tool arranges it (imatrix.cpp compute_imatrix)
+        m.forward(chunk, m.new_cache(n_ctx))
         log(f"[{c + 1}/{n_chunks}] {len(col.sum2)} matrices")
     m.observer = None
     return col, n_chunks
@@ -91,6 +100,7 @@ def main(argv=None):
     ap.add_argument("-o", "--output", default="imatrix.gguf")
     ap.add_argument("-c", "--ctx-size", type=int, default=128)
     ap.add_argument("--chunks", type=int, default=-1)
+    ap.add_argument("--process-output", action="store_true", help="also collect statistics for output.weight")
     a = ap.parse_args(argv)
     from distributed_llm_pipeline_b200.utils.tokenizer import Tokenizer
     f = open_gguf(a.model)
@@ -99,7 +109,7 @@ def main(argv=None):
     else:
         g = torch.Generator().manual_seed(0)
         ids = torch.randint(3, len(f.metadata["tokenizer.ggml.tokens"]), (a.ctx_size * max(1, a.chunks if a.chunks > 0 else 4),), generator=g).tolist()
-    col, n = collect(a.model, ids, a.ctx_size, a.chunks)
+    col, n = collect(a.model, ids, a.ctx_size, a.chunks, process_output=a.process_output)
     save(a.output, col, n, a.ctx_size, a.file or "synthetic")
     print(f"{a.output}: {len(col.sum2)} matrices, {n} chunks of {a.ctx_size} tokens")
 
