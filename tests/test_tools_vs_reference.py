@@ -118,3 +118,25 @@ def test_export_lora_merges_like_the_reference(tmp_models, tmp_path):
         assert np.abs(a - b).max() < 2e-3, n
         if n in deltas:
             assert np.abs(a - s.array(n)).max() > 1e-2           # the adapter really was merged
+
+
+@pytest.mark.parametrize("method,floor", [("mean", 0.99999), ("pca", 0.9)])      # the power iteration stops short of the exact axis when eigenvalues are close
+def test_cvector_generator_finds_the_same_directions(tmp_path, method, floor):
+    """Same prompt pairs, same model: `dlp_cvector.py` and `llama-cvector-generator` write the same unit directions (PCA up to sign:
+    a principal axis has none; the reference iterates a power method, here the SVD is exact)."""
+    from distributed_llm_pipeline_b200.gguf import write_synthetic_gguf
+    from distributed_llm_pipeline_b200.models.config import preset
+    model = write_synthetic_gguf(str(tmp_path / "m.gguf"), preset("tiny-smollm3"), "F16", seed=1)
+    (tmp_path / "pos.txt").write_text("I am very happy today\nthis is wonderful news\nwhat a lovely bright morning\n")
+    (tmp_path / "neg.txt").write_text("I am very sad today\nthis is terrible news\nwhat a gloomy dark evening\n")
+    run([tool("llama-cvector-generator"), "-m", model, "--positive-file", str(tmp_path / "pos.txt"), "--negative-file", str(tmp_path / "neg.txt"), "--method", method,
+         "-o", str(tmp_path / "ref.gguf"), "-t", "2", "--pca-iter", "2000", "--pca-batch", "100"], cwd=str(tmp_path))
+    ours("dlp_cvector.py", "-m", model, "--positive-file", str(tmp_path / "pos.txt"), "--negative-file", str(tmp_path / "neg.txt"), "--method", method,
+         "-o", str(tmp_path / "ours.gguf"), "--device", "cpu")
+    r, o = open_gguf(str(tmp_path / "ref.gguf")), open_gguf(str(tmp_path / "ours.gguf"))
+    assert sorted(r.tensors) == sorted(o.tensors) == ["direction.1", "direction.2", "direction.3"]
+    assert r.metadata["controlvector.model_hint"] == o.metadata["controlvector.model_hint"] and r.metadata["controlvector.layer_count"] == o.metadata["controlvector.layer_count"]
+    for n in r.tensors:
+        a, b = np.asarray(r.array(n)).reshape(-1), np.asarray(o.array(n)).reshape(-1)
+        cos = float(a @ b / np.linalg.norm(a) / np.linalg.norm(b))
+        assert (cos if method == "mean" else abs(cos)) > floor, (n, cos)
