@@ -120,15 +120,24 @@ def test_export_lora_merges_like_the_reference(tmp_models, tmp_path):
             assert np.abs(a - s.array(n)).max() > 1e-2           # the adapter really was merged
 
 
-@pytest.mark.parametrize("method,floor", [("mean", 0.99999), ("pca", 0.9)])      # the power iteration stops short of the exact axis when eigenvalues are close
-def test_cvector_generator_finds_the_same_directions(tmp_path, method, floor):
-    """Same prompt pairs, same model: `dlp_cvector.py` and `llama-cvector-generator` write the same unit directions (PCA up to sign:
-    a principal axis has none; the reference iterates a power method, here the SVD is exact)."""
+@pytest.mark.parametrize("method", ["mean", "pca"])
+def test_cvector_generator_finds_the_same_directions(tmp_path, method):
+    """Same prompt pairs, same model: `dlp_cvector.py` and `llama-cvector-generator` write the same unit directions for `mean`; for `pca` the
+    reference runs a randomly started power iteration, so the comparison is by what counts - the share of the difference energy along the
+    direction: the exact SVD here must capture at least as much as the reference's vector."""
+    import torch
+
+    import dlp_cvector
     from distributed_llm_pipeline_b200.gguf import write_synthetic_gguf
     from distributed_llm_pipeline_b200.models.config import preset
+    from distributed_llm_pipeline_b200.models.llama import LlamaEngine
+    from distributed_llm_pipeline_b200.models.weights import load_weights
+    from distributed_llm_pipeline_b200.utils.tokenizer import Tokenizer
     model = write_synthetic_gguf(str(tmp_path / "m.gguf"), preset("tiny-smollm3"), "F16", seed=1)
-    (tmp_path / "pos.txt").write_text("I am very happy today\nthis is wonderful news\nwhat a lovely bright morning\n")
-    (tmp_path / "neg.txt").write_text("I am very sad today\nthis is terrible news\nwhat a gloomy dark evening\n")
+    pos = ["I am very happy today", "this is wonderful news", "what a lovely bright morning"]
+    neg = ["I am very sad today", "this is terrible news", "what a gloomy dark evening"]
+    (tmp_path / "pos.txt").write_text("\n".join(pos) + "\n")
+    (tmp_path / "neg.txt").write_text("\n".join(neg) + "\n")
     run([tool("llama-cvector-generator"), "-m", model, "--positive-file", str(tmp_path / "pos.txt"), "--negative-file", str(tmp_path / "neg.txt"), "--method", method,
          "-o", str(tmp_path / "ref.gguf"), "-t", "2", "--pca-iter", "2000", "--pca-batch", "100"], cwd=str(tmp_path))
     ours("dlp_cvector.py", "-m", model, "--positive-file", str(tmp_path / "pos.txt"), "--negative-file", str(tmp_path / "neg.txt"), "--method", method,
@@ -136,7 +145,14 @@ def test_cvector_generator_finds_the_same_directions(tmp_path, method, floor):
     r, o = open_gguf(str(tmp_path / "ref.gguf")), open_gguf(str(tmp_path / "ours.gguf"))
     assert sorted(r.tensors) == sorted(o.tensors) == ["direction.1", "direction.2", "direction.3"]
     assert r.metadata["controlvector.model_hint"] == o.metadata["controlvector.model_hint"] and r.metadata["controlvector.layer_count"] == o.metadata["controlvector.layer_count"]
-    for n in r.tensors:
-        a, b = np.asarray(r.array(n)).reshape(-1), np.asarray(o.array(n)).reshape(-1)
-        cos = float(a @ b / np.linalg.norm(a) / np.linalg.norm(b))
-        assert (cos if method == "mean" else abs(cos)) > floor, (n, cos)
+    eng = LlamaEngine(load_weights(model, "cpu"), n_ctx=64, max_seqs=1, page_size=16, max_batch_tokens=64)
+    rows = dlp_cvector.difference_rows(eng, Tokenizer.from_gguf(model), pos, neg, log=lambda s: None)
+    for il, n in enumerate(sorted(r.tensors)):
+        a, b = torch.from_numpy(np.asarray(r.array(n)).reshape(-1).copy()), torch.from_numpy(np.asarray(o.array(n)).reshape(-1).copy())
+        assert abs(float(b.norm()) - 1) < 1e-3
+        a = a / a.norm()             # the reference's power iteration does not always return a unit vector
+        if method == "mean":
+            assert float(a @ b) > 0.99999, (n, float(a @ b))
+        else:
+            ea, eb = float((rows[il] @ a).pow(2).sum()), float((rows[il] @ b).pow(2).sum())
+            assert eb >= 0.999 * ea, (n, ea, eb)       # ours is the optimum; the reference's randomly started iteration lands at or below it

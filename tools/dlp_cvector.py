@@ -50,11 +50,12 @@ def directions(diffs: list[torch.Tensor], method: str) -> list[torch.Tensor]:
     return out
 
 
-def generate(eng, tok, positive: list[str], negative: list[str], method: str = "pca", log=print) -> list[torch.Tensor]:
+def difference_rows(eng, tok, positive: list[str], negative: list[str], log=print) -> list[torch.Tensor]:
+    """Per layer (all but the last, which the reference ignores too): the non-zero rows of (positive - negative) layer outputs, [m, E]."""
     if len(positive) != len(negative) or not positive:
         raise SystemExit("need the same (non-zero) number of positive and negative prompts")
     n_layer = eng.cfg.n_layer
-    rows: list[list[torch.Tensor]] = [[] for _ in range(n_layer - 1)]      # the final layer is ignored, as in the reference
+    rows: list[list[torch.Tensor]] = [[] for _ in range(n_layer - 1)]
     pad = tok.encode(" ", add_bos=False)[-1:] or [0]
     for i, (p, n) in enumerate(zip(positive, negative)):
         a, b = tok.encode(p), tok.encode(n)
@@ -65,7 +66,11 @@ def generate(eng, tok, positive: list[str], negative: list[str], method: str = "
             d = ha[il] - hb[il]
             rows[il].append(d[d.abs().sum(-1) > 0])
         log(f"pair {i + 1}/{len(positive)}: {T} tokens")
-    return directions([torch.cat(r) for r in rows], method)
+    return [torch.cat(r) for r in rows]
+
+
+def generate(eng, tok, positive: list[str], negative: list[str], method: str = "pca", log=print) -> list[torch.Tensor]:
+    return directions(difference_rows(eng, tok, positive, negative, log), method)
 
 
 def save(path: str, dirs: list[torch.Tensor], model_hint: str) -> str:
