@@ -165,7 +165,7 @@ def _tensor_plan(cfg: ModelConfig, rope_freqs: bool):
             plan.append((p + "post_attention_norm.weight", (E,), il, 0.0))
         if cfg.norm_type == "layer":
             plan += norm(p + "ffn_norm", il, nl["ffn"])
-        elif cfg.pre_norm:
+        elif cfg.pre_norm and not (cfg.parallel_residual and cfg.arch == "plamo"):
             plan.append((p + cfg.ffn_norm_name, (E,), il, 0.0))
         if cfg.ffn_act in ("gelu", "relu2"):       # non-gated MLP
             plan += [(p + "ffn_up.weight", (F, E), il, 0.02), (p + "ffn_down.weight", (E, F), il, 0.02)]

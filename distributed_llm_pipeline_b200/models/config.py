@@ -205,6 +205,10 @@ PRESETS: dict[str, ModelConfig] = {
                                  n_ff=512, n_ctx_train=512, rope_theta=10000.0, rope_dim=64),
     "tiny-pangu": ModelConfig(name="tiny-pangu", arch="pangu-embedded", vocab_size=512, n_embd=256, n_layer=2, n_head=4, n_head_kv=2, head_dim=64,
                               n_ff=512, n_ctx_train=512, rope_theta=10000.0, rope_dim=64, rope_neox=True, qkv_bias=True, attn_out_bias=True),
+    "tiny-chatglm": ModelConfig(name="tiny-chatglm", arch="chatglm", vocab_size=512, n_embd=256, n_layer=2, n_head=4, n_head_kv=2, head_dim=64, n_ff=512,
+                                n_ctx_train=512, rope_theta=10000.0, rope_dim=32, fused_qkv=True, qkv_bias=True, fused_gate_up=True),
+    "tiny-plamo": ModelConfig(name="tiny-plamo", arch="plamo", vocab_size=512, n_embd=256, n_layer=2, n_head=4, n_head_kv=4, head_dim=64, n_ff=512,
+                              n_ctx_train=512, rope_theta=10000.0, rope_dim=64, rope_neox=True, parallel_residual=True),
     "tiny-command-r": ModelConfig(name="tiny-command-r", arch="command-r", vocab_size=512, n_embd=256, n_layer=2, n_head=4, n_head_kv=2,
                                   head_dim=64, n_ff=512, n_ctx_train=512, rope_theta=10000.0, rope_dim=64, norm_type="layer",
                                   parallel_residual=True, logit_scale=16.0, tie_embeddings=True),
@@ -244,8 +248,8 @@ PRESETS: dict[str, ModelConfig] = {
 SUPPORTED_ARCHS = {"llama", "qwen2", "qwen2moe", "qwen3", "qwen3moe", "phi3", "granite",
                    "internlm2", "xverse", "ernie4_5", "exaone", "seed_oss", "minicpm", "granitemoe", "smollm3",
                    "starcoder2", "falcon", "olmo", "orion", "command-r", "gptneox", "stablelm", "nemotron", "arcee",
-                   "gpt2", "starcoder", "codeshell", "qwen", "baichuan", "olmo2", "glm4", "mistral3", "pangu-embedded"}
-ROPE_NORM_ARCHS = {"llama", "granite", "granitemoe", "minicpm", "internlm2", "xverse", "ernie4_5", "smollm3", "olmo", "command-r", "arcee", "baichuan", "glm4", "mistral3"}     # llama_model_rope_type
+                   "gpt2", "starcoder", "codeshell", "qwen", "baichuan", "olmo2", "glm4", "mistral3", "pangu-embedded", "chatglm", "plamo"}
+ROPE_NORM_ARCHS = {"llama", "granite", "granitemoe", "minicpm", "internlm2", "xverse", "ernie4_5", "smollm3", "olmo", "command-r", "arcee", "baichuan", "glm4", "mistral3", "chatglm"}     # llama_model_rope_type
 # LayerNorm families and what differs beyond the norm (llama.cpp/src/models/{starcoder2,falcon,olmo,orion,command-r}.cpp):
 #   starcoder2: biases on every matrix, non-gated GELU MLP;  falcon: fused QKV, GELU MLP, attention and MLP in parallel from the same
 #   (or a second) norm;  olmo: norms without parameters;  orion: llama with LayerNorm;  command-r: parallel, logits * logit_scale
@@ -315,8 +319,8 @@ def config_from_gguf(meta: dict[str, Any], tensors: dict | None = None) -> Model
         norm_type="layer" if arch in LAYERNORM_ARCHS else "rms", ffn_act="gelu" if arch in ("starcoder2", "falcon", "gptneox", "gpt2", "starcoder", "codeshell") else "relu2" if arch in ("nemotron", "arcee") else "swiglu",
         attn_out_bias=tensors is not None and "blk.0.attn_output.bias" in tensors and arch not in LAYERNORM_ARCHS,
         post_norm=arch in ("olmo2", "glm4"), pre_norm=arch != "olmo2", qk_norm_full=arch == "olmo2",
-        parallel_residual=arch in ("falcon", "command-r") or (arch == "gptneox" and bool(g("use_parallel_residual", True)))
-        or (arch == "stablelm" and tensors is not None and "blk.0.ffn_norm.weight" not in tensors), fused_gate_up=arch in ("phi3", "glm4"), rope_theta=float(g("rope.freq_base", 10000.0)),
+        parallel_residual=arch in ("falcon", "command-r", "plamo") or (arch == "gptneox" and bool(g("use_parallel_residual", True)))
+        or (arch == "stablelm" and tensors is not None and "blk.0.ffn_norm.weight" not in tensors), fused_gate_up=arch in ("phi3", "glm4", "chatglm"), rope_theta=float(g("rope.freq_base", 10000.0)),
         rope_dim=int(g("rope.dimension_count", head_dim)), rope_neox=arch not in ROPE_NORM_ARCHS, rope_scale_linear=scale,
         embedding_scale=float(g("embedding_scale") or dflt["embedding_scale"]), residual_scale=float(g("residual_scale") or dflt["residual_scale"]),
         logit_scale=(1.0 / float(g("logit_scale") or 1.0)) if arch == "command-r" else float(g("logit_scale") or dflt["logit_scale"]), attention_scale=float(g("attention.scale", 0.0) or 0.0),
