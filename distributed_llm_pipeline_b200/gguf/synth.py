@@ -173,6 +173,9 @@ def _tensor_plan(cfg: ModelConfig, rope_freqs: bool):
                 plan += [(p + "ffn_up.bias", (F,), il, 0.05), (p + "ffn_down.bias", (E,), il, 0.05)]
         elif cfg.fused_gate_up:
             plan += [(p + "ffn_up.weight", (2 * F, E), il, 0.02), (p + "ffn_down.weight", (E, F), il, 0.02)]
+        elif cfg.is_moe and il < cfg.n_layer_dense_lead:      # deepseek / bailingmoe: dense lead layers with their own width
+            Fd = cfg.n_ff_dense or F
+            plan += [(p + "ffn_gate.weight", (Fd, E), il, 0.02), (p + "ffn_down.weight", (E, Fd), il, 0.02), (p + "ffn_up.weight", (Fd, E), il, 0.02)]
         elif cfg.is_moe:
             plan += [
                 (p + "ffn_gate_inp.weight", (cfg.n_expert, E), il, 0.02),
@@ -182,8 +185,9 @@ def _tensor_plan(cfg: ModelConfig, rope_freqs: bool):
             ]
             if cfg.n_ff_shared:     # qwen2moe shared expert + its scalar gate
                 Fs = cfg.n_ff_shared
-                plan += [(p + "ffn_gate_inp_shexp.weight", (E,), il, 0.0),
-                         (p + "ffn_gate_shexp.weight", (Fs, E), il, 0.02), (p + "ffn_up_shexp.weight", (Fs, E), il, 0.02),
+                if cfg.arch == "qwen2moe":
+                    plan.append((p + "ffn_gate_inp_shexp.weight", (E,), il, 0.0))
+                plan += [(p + "ffn_gate_shexp.weight", (Fs, E), il, 0.02), (p + "ffn_up_shexp.weight", (Fs, E), il, 0.02),
                          (p + "ffn_down_shexp.weight", (E, Fs), il, 0.02)]
         else:
             plan += [
@@ -215,7 +219,7 @@ def write_synthetic_gguf(path: str, cfg: ModelConfig, ftype: str = "F16", seed: 
     w.add(f"{a}.context_length", cfg.n_ctx_train, ValueType.UINT32)
     w.add(f"{a}.embedding_length", cfg.n_embd, ValueType.UINT32)
     w.add(f"{a}.block_count", cfg.n_layer, ValueType.UINT32)
-    w.add(f"{a}.feed_forward_length", cfg.n_ff * (2 if a == "qwen" else 1), ValueType.UINT32)
+    w.add(f"{a}.feed_forward_length", (cfg.n_ff_dense or cfg.n_ff) * (2 if a == "qwen" else 1), ValueType.UINT32)
     w.add(f"{a}.attention.head_count", cfg.n_head, ValueType.UINT32)
     w.add(f"{a}.attention.head_count_kv", cfg.n_head_kv, ValueType.UINT32)
     w.add(f"{a}.attention.layer_norm_epsilon" if cfg.norm_type == "layer" else f"{a}.attention.layer_norm_rms_epsilon", float(cfg.rms_eps), ValueType.FLOAT32)
@@ -246,8 +250,14 @@ def write_synthetic_gguf(path: str, cfg: ModelConfig, ftype: str = "F16", seed: 
             w.add(f"{a}.expert_feed_forward_length", cfg.n_ff, ValueType.UINT32)
         w.add(f"{a}.expert_count", cfg.n_expert, ValueType.UINT32)
         w.add(f"{a}.expert_used_count", cfg.n_expert_used, ValueType.UINT32)
-        if cfg.n_ff_shared:
+        if cfg.n_ff_shared and a not in ("deepseek", "bailingmoe"):
             w.add(f"{a}.expert_shared_feed_forward_length", cfg.n_ff_shared, ValueType.UINT32)
+        if a in ("deepseek", "bailingmoe"):
+            w.add(f"{a}.leading_dense_block_count", cfg.n_layer_dense_lead, ValueType.UINT32)
+            w.add(f"{a}.expert_shared_count", cfg.n_ff_shared // cfg.n_ff, ValueType.UINT32)
+            w.add(f"{a}.expert_weights_scale", float(cfg.expert_weights_scale), ValueType.FLOAT32)
+            if a == "bailingmoe":
+                w.add(f"{a}.expert_weights_norm", bool(cfg.moe_norm_topk))
     if vocab:
         toks, scores, types = synthetic_vocab(cfg.vocab_size)
         w.add("tokenizer.ggml.model", "llama")

@@ -50,7 +50,12 @@ class ModelConfig:
     attention_scale: float = 0.0   # replaces 1/sqrt(head_dim) when > 0
     # qwen2moe: routed experts without re-normalised top-k weights plus an always-on shared expert behind a sigmoid gate
     moe_norm_topk: bool = True     # renormalise the selected experts' weights (Mixtral, qwen3moe); qwen2moe: False
-    n_ff_shared: int = 0           # > 0: shared-expert FFN width (`ffn_*_shexp`, gate vector `ffn_gate_inp_shexp`)
+    n_ff_shared: int = 0           # > 0: shared-expert FFN width (`ffn_*_shexp`; qwen2moe also has the gate vector `ffn_gate_inp_shexp`)
+    # deepseek (v1), bailingmoe: the first layers are dense (their own FFN width), routed weights are multiplied by a constant, and the
+    # shared experts are added without a gate (`llama.cpp/src/models/deepseek.cpp:86-120`)
+    n_layer_dense_lead: int = 0
+    n_ff_dense: int = 0            # FFN width of the dense lead layers (0: n_ff)
+    expert_weights_scale: float = 1.0      # read and written back, not applied: the reference's builders for these two families pass scale_w = false
     # LayerNorm / GELU / parallel-residual families (starcoder2, falcon, olmo, orion, command-r): the generic layer path
     norm_type: str = "rms"         # "rms" | "layer" (mean-centred; weight and bias optional per file: olmo has neither)
     ffn_act: str = "swiglu"        # "swiglu" (gated SiLU) | "gelu" | "relu2" (non-gated: ffn_up -> activation -> ffn_down, biases optional)
@@ -209,6 +214,12 @@ PRESETS: dict[str, ModelConfig] = {
                                 n_ctx_train=512, rope_theta=10000.0, rope_dim=32, fused_qkv=True, qkv_bias=True, fused_gate_up=True),
     "tiny-plamo": ModelConfig(name="tiny-plamo", arch="plamo", vocab_size=512, n_embd=256, n_layer=2, n_head=4, n_head_kv=4, head_dim=64, n_ff=512,
                               n_ctx_train=512, rope_theta=10000.0, rope_dim=64, rope_neox=True, parallel_residual=True),
+    "tiny-deepseek": ModelConfig(name="tiny-deepseek", arch="deepseek", vocab_size=512, n_embd=256, n_layer=3, n_head=4, n_head_kv=4, head_dim=64, n_ff=128,
+                                 n_ctx_train=512, rope_theta=10000.0, rope_dim=64, n_expert=4, n_expert_used=2, moe_norm_topk=False, n_ff_shared=256,
+                                 n_layer_dense_lead=1, n_ff_dense=512, expert_weights_scale=1.5),
+    "tiny-bailingmoe": ModelConfig(name="tiny-bailingmoe", arch="bailingmoe", vocab_size=512, n_embd=256, n_layer=2, n_head=4, n_head_kv=2, head_dim=64, n_ff=128,
+                                   n_ctx_train=512, rope_theta=10000.0, rope_dim=64, n_expert=4, n_expert_used=2, moe_norm_topk=True, n_ff_shared=128,
+                                   expert_weights_scale=2.0),
     "tiny-command-r": ModelConfig(name="tiny-command-r", arch="command-r", vocab_size=512, n_embd=256, n_layer=2, n_head=4, n_head_kv=2,
                                   head_dim=64, n_ff=512, n_ctx_train=512, rope_theta=10000.0, rope_dim=64, norm_type="layer",
                                   parallel_residual=True, logit_scale=16.0, tie_embeddings=True),
@@ -248,8 +259,8 @@ PRESETS: dict[str, ModelConfig] = {
 SUPPORTED_ARCHS = {"llama", "qwen2", "qwen2moe", "qwen3", "qwen3moe", "phi3", "granite",
                    "internlm2", "xverse", "ernie4_5", "exaone", "seed_oss", "minicpm", "granitemoe", "smollm3",
                    "starcoder2", "falcon", "olmo", "orion", "command-r", "gptneox", "stablelm", "nemotron", "arcee",
-                   "gpt2", "starcoder", "codeshell", "qwen", "baichuan", "olmo2", "glm4", "mistral3", "pangu-embedded", "chatglm", "plamo"}
-ROPE_NORM_ARCHS = {"llama", "granite", "granitemoe", "minicpm", "internlm2", "xverse", "ernie4_5", "smollm3", "olmo", "command-r", "arcee", "baichuan", "glm4", "mistral3", "chatglm"}     # llama_model_rope_type
+                   "gpt2", "starcoder", "codeshell", "qwen", "baichuan", "olmo2", "glm4", "mistral3", "pangu-embedded", "chatglm", "plamo", "deepseek", "bailingmoe"}
+ROPE_NORM_ARCHS = {"llama", "granite", "granitemoe", "minicpm", "internlm2", "xverse", "ernie4_5", "smollm3", "olmo", "command-r", "arcee", "baichuan", "glm4", "mistral3", "chatglm", "deepseek", "bailingmoe"}     # llama_model_rope_type
 # LayerNorm families and what differs beyond the norm (llama.cpp/src/models/{starcoder2,falcon,olmo,orion,command-r}.cpp):
 #   starcoder2: biases on every matrix, non-gated GELU MLP;  falcon: fused QKV, GELU MLP, attention and MLP in parallel from the same
 #   (or a second) norm;  olmo: norms without parameters;  orion: llama with LayerNorm;  command-r: parallel, logits * logit_scale
@@ -325,7 +336,10 @@ def config_from_gguf(meta: dict[str, Any], tensors: dict | None = None) -> Model
         embedding_scale=float(g("embedding_scale") or dflt["embedding_scale"]), residual_scale=float(g("residual_scale") or dflt["residual_scale"]),
         logit_scale=(1.0 / float(g("logit_scale") or 1.0)) if arch == "command-r" else float(g("logit_scale") or dflt["logit_scale"]), attention_scale=float(g("attention.scale", 0.0) or 0.0),
         no_rope_step=4 if arch == "smollm3" else 1 if arch in LEARNED_POS_ARCHS else 0, learned_pos=arch in LEARNED_POS_ARCHS,
-        moe_norm_topk=arch != "qwen2moe", n_ff_shared=int(g("expert_shared_feed_forward_length", 0) or 0),
+        moe_norm_topk=bool(g("expert_weights_norm", False)) if arch == "bailingmoe" else arch not in ("qwen2moe", "deepseek"),
+        n_ff_shared=int(g("expert_shared_feed_forward_length", 0) or 0) or (int(g("expert_shared_count", 0) or 0) * int(g("expert_feed_forward_length", 0) or 0)),
+        n_layer_dense_lead=int(g("leading_dense_block_count", 0) or 0), expert_weights_scale=float(g("expert_weights_scale", 1.0) or 1.0),
+        n_ff_dense=int(g("feed_forward_length")) if int(g("leading_dense_block_count", 0) or 0) > 0 else 0,
         qkv_bias=arch in ("qwen2", "qwen2moe") or (tensors is not None and ("blk.0.attn_q.bias" in tensors or "blk.0.attn_qkv.bias" in tensors)),
         qk_norm=arch in ("qwen3", "qwen3moe") or (arch != "olmo2" and tensors is not None and "blk.0.attn_q_norm.weight" in tensors),
         fused_qkv=arch == "phi3" or (tensors is not None and "blk.0.attn_qkv.weight" in tensors),

@@ -142,7 +142,8 @@ class LlamaEngine:
         self.qkv16 = torch.zeros(M, qkv_dim, dtype=f16, device=dev)
         self.q = torch.zeros(M, self.Hq * self.D, dtype=f16, device=dev)
         self.att = torch.zeros(M, self.Hq * self.D, dtype=f16, device=dev)
-        self.act = torch.zeros(M, self.F, dtype=f16, device=dev)
+        f_buf = max(self.F, (cfg.n_ff_dense // max(1, self.comm.tp_size)) if cfg.n_layer_dense_lead else 0)     # dense lead layers may be wider than the experts
+        self.act = torch.zeros(M, f_buf, dtype=f16, device=dev)
         # generic layer path: fp32 MLP pre-activation (bias + GELU run between the two mat-muls), second norm output (falcon-40b)
         self.up32 = torch.zeros(M, self.F, dtype=f32, device=dev) if cfg.ffn_act != "swiglu" else None
         self.xn2 = torch.zeros(M, self.E, dtype=f16, device=dev) if cfg.post_norm or any(
@@ -335,7 +336,7 @@ class LlamaEngine:
             ops.linear(lw.wo, att, "add", out=h, scratch=self._scratch_for(lw.wo))
             xn = ops.rmsnorm(h, lw.ffn_norm, cfg.rms_eps, out=self.xn[:T])
         # --- feed-forward block ---
-        if cfg.is_moe:
+        if lw.router is not None:       # (a mixture-of-experts model may still have dense layers: deepseek's lead layers)
             self._moe(lw, T, None if small else xn)
             return
         if small:
@@ -456,10 +457,10 @@ class LlamaEngine:
         if cfg.moe_norm_topk:
             topw = topw / topw.sum(-1, keepdim=True)
         out = torch.zeros(T, self.E, dtype=torch.float32, device=h.device)
-        if lw.shared_gate is not None:   # qwen2moe: always-on shared expert behind a sigmoid gate (partial sums under TP: the
-            act = ops.linear(lw.w_gate, xn, "swiglu", w_up=lw.w_up, scratch=self._scratch_for(lw.w_gate, lw.w_up))   # gate is replicated)
+        if lw.w_gate is not None:        # always-on shared expert: behind a sigmoid gate (qwen2moe) or added as it is (deepseek, bailingmoe);
+            act = ops.linear(lw.w_gate, xn, "swiglu", w_up=lw.w_up, scratch=self._scratch_for(lw.w_gate, lw.w_up))   # partial sums under TP, the gate is replicated
             ys = ops.linear(lw.w_down, act, "f32", scratch=self._scratch_for(lw.w_down))
-            out += torch.sigmoid(xn.float() @ lw.shared_gate)[:, None] * ys
+            out += (torch.sigmoid(xn.float() @ lw.shared_gate)[:, None] * ys) if lw.shared_gate is not None else ys
         topi_h = topi.cpu()
         for e in torch.unique(topi_h).tolist():
             rows = (topi_h == e).any(-1).nonzero().flatten().to(h.device)
@@ -507,10 +508,13 @@ class LlamaEngine:
             tgt = self.delta[:T]
             tgt.zero_()
         ops.moe_combine(b["y"][:A], b["plan"], b["w"][:A], T, k, tgt)
-        if lw.shared_gate is not None:   # qwen2moe: always-on shared expert behind a sigmoid gate (device ops, no sync)
+        if lw.w_gate is not None:        # always-on shared expert, gated (qwen2moe) or not (deepseek, bailingmoe): device ops, no sync
             act = ops.linear(lw.w_gate, xn, "swiglu", w_up=lw.w_up)
             ys = ops.linear(lw.w_down, act, "f32")
-            tgt.addcmul_(torch.sigmoid(xn.float() @ lw.shared_gate)[:, None], ys)
+            if lw.shared_gate is not None:
+                tgt.addcmul_(torch.sigmoid(xn.float() @ lw.shared_gate)[:, None], ys)
+            else:
+                tgt.add_(ys)
         if tp:
             h.add_(comm.allreduce_delta(tgt, -1, 1))
 
@@ -840,7 +844,8 @@ class LlamaEngine:
             self.next_tok[:B].copy_(torch.as_tensor(tokens, dtype=torch.int32), non_blocking=True)
         if hidden_in is not None:
             self.h[:B].copy_(hidden_in)
-        moe_host = self.cfg.is_moe and not self._moe_grouped_ok(next(iter(self.w.layers.values())))   # routing through the host: no graph
+        moe_lw = next((lw for lw in self.w.layers.values() if lw.router is not None), None)
+        moe_host = moe_lw is not None and not self._moe_grouped_ok(moe_lw)   # routing through the host: no graph
         graphable = (use_graph and self.eval_callback is None and self.device.type == "cuda" and not moe_host
                      and not getattr(self.comm, "no_graph", False)    # (the sequence-parallel path is capturable too: its epochs are
                      and not (self.sp_ok and B > 4 and os.environ.get("DLP_SP_GRAPH", "1") == "0"))   # positions inside the pass on top of a device-side counter; DLP_SP_GRAPH=0: A/B)

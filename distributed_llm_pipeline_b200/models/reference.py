@@ -182,7 +182,7 @@ class ReferenceModel:
         if c.fused_gate_up:   # phi3: ffn_up holds [gate | up]; swiglu = silu(first half) * second half
             g, u = self.mm(x, p + "ffn_up.weight").split([c.n_ff, c.n_ff], dim=-1)
             return self.mm(torch.nn.functional.silu(g) * u, p + "ffn_down.weight")
-        if not c.is_moe:
+        if not c.is_moe or p + "ffn_gate_inp.weight" not in w:      # dense model, or one of the dense lead layers of deepseek / bailingmoe
             g = self.mm(x, p + "ffn_gate.weight")
             u = self.mm(x, p + "ffn_up.weight")
             return self.mm(torch.nn.functional.silu(g) * u, p + "ffn_down.weight")
@@ -196,7 +196,8 @@ class ReferenceModel:
             g = self.mm(x, p + "ffn_gate_shexp.weight")
             u = self.mm(x, p + "ffn_up_shexp.weight")
             sh = self.mm(torch.nn.functional.silu(g) * u, p + "ffn_down_shexp.weight")
-            out = out + torch.sigmoid(x @ w[p + "ffn_gate_inp_shexp.weight"].reshape(-1, 1)) * sh
+            gate = torch.sigmoid(x @ w[p + "ffn_gate_inp_shexp.weight"].reshape(-1, 1)) if p + "ffn_gate_inp_shexp.weight" in w else 1.0
+            out = out + gate * sh
         for e in range(c.n_expert):
             sel = (topi == e)
             rows = sel.any(-1).nonzero().flatten()

@@ -278,7 +278,7 @@ def load_weights(src: str | GGUFModelFiles, device, layer_range: range | None = 
             lw.w_gate = mat(p + "ffn_up.weight", rows=(f0, f1))
             lw.w_up = mat(p + "ffn_up.weight", rows=(cfg.n_ff + f0, cfg.n_ff + f1))
             lw.w_down = mat(p + "ffn_down.weight", cols=(f0, f1), scale=cfg.residual_scale)
-        elif cfg.is_moe:
+        elif cfg.is_moe and p + "ffn_gate_inp.weight" in f:
             lw.router = f32(p + "ffn_gate_inp.weight")
             for e in range(cfg.n_expert):
                 lw.e_gate.append(mat(p + "ffn_gate_exps.weight", rows=(f0, f1), sub=e))
@@ -304,8 +304,11 @@ def load_weights(src: str | GGUFModelFiles, device, layer_range: range | None = 
                 lw.w_gate = mat(p + "ffn_gate_shexp.weight", rows=(s0, s1))
                 lw.w_up = mat(p + "ffn_up_shexp.weight", rows=(s0, s1))
                 lw.w_down = mat(p + "ffn_down_shexp.weight", cols=(s0, s1), scale=cfg.residual_scale)
-                lw.shared_gate = f32(p + "ffn_gate_inp_shexp.weight").reshape(-1)
+                if p + "ffn_gate_inp_shexp.weight" in f:      # qwen2moe gates it; deepseek / bailingmoe add it as it is
+                    lw.shared_gate = f32(p + "ffn_gate_inp_shexp.weight").reshape(-1)
         else:
+            if cfg.is_moe:        # a dense lead layer of a mixture-of-experts model: its own FFN width
+                f0, f1 = _split(cfg.n_ff_dense or cfg.n_ff, tp_size, tp_rank, 256 if tp_size > 1 else 1)
             lw.w_gate = mat(p + "ffn_gate.weight", rows=(f0, f1))
             lw.w_up = mat(p + "ffn_up.weight", rows=(f0, f1))
             lw.w_down = mat(p + "ffn_down.weight", cols=(f0, f1), scale=cfg.residual_scale)
