@@ -245,6 +245,11 @@ def write_synthetic_gguf(path: str, cfg: ModelConfig, ftype: str = "F16", seed: 
         w.add(f"{a}.rope.scaling.factor", float(1.0 / cfg.rope_scale_linear), ValueType.FLOAT32)
     if a == "gptneox":
         w.add(f"{a}.use_parallel_residual", bool(cfg.parallel_residual))
+    if a == "qwen3vl":
+        w.add(f"{a}.n_deepstack_layers", 0, ValueType.UINT32)
+    if a in ("qwen2vl", "qwen3vl"):      # temporal / height / width / extra shares of the rotary pairs (text tokens use one position for all of them)
+        q = cfg.rope_dim // 8
+        w.add(f"{a}.rope.dimension_sections", np.asarray([q, (cfg.rope_dim // 2 - q) // 2, cfg.rope_dim // 2 - q - (cfg.rope_dim // 2 - q) // 2, 0], np.int32), etype=ValueType.INT32)
     if cfg.is_moe:
         if a != "llama":
             w.add(f"{a}.expert_feed_forward_length", cfg.n_ff, ValueType.UINT32)

@@ -220,6 +220,11 @@ PRESETS: dict[str, ModelConfig] = {
     "tiny-bailingmoe": ModelConfig(name="tiny-bailingmoe", arch="bailingmoe", vocab_size=512, n_embd=256, n_layer=2, n_head=4, n_head_kv=2, head_dim=64, n_ff=128,
                                    n_ctx_train=512, rope_theta=10000.0, rope_dim=64, n_expert=4, n_expert_used=2, moe_norm_topk=True, n_ff_shared=128,
                                    expert_weights_scale=2.0),
+    # qwen2vl, text only: multi-section rotary with the same position in every section is the plain half-split rotation
+    "tiny-qwen2vl": ModelConfig(name="tiny-qwen2vl", arch="qwen2vl", vocab_size=512, n_embd=256, n_layer=2, n_head=4, n_head_kv=2, head_dim=64, n_ff=512,
+                                n_ctx_train=512, rope_theta=10000.0, rope_dim=64, rope_neox=True, qkv_bias=True),
+    "tiny-qwen3vl": ModelConfig(name="tiny-qwen3vl", arch="qwen3vl", vocab_size=512, n_embd=256, n_layer=2, n_head=4, n_head_kv=2, head_dim=64, n_ff=512,
+                                n_ctx_train=512, rope_theta=10000.0, rope_dim=64, rope_neox=True, qk_norm=True),
     "tiny-command-r": ModelConfig(name="tiny-command-r", arch="command-r", vocab_size=512, n_embd=256, n_layer=2, n_head=4, n_head_kv=2,
                                   head_dim=64, n_ff=512, n_ctx_train=512, rope_theta=10000.0, rope_dim=64, norm_type="layer",
                                   parallel_residual=True, logit_scale=16.0, tie_embeddings=True),
@@ -259,7 +264,7 @@ PRESETS: dict[str, ModelConfig] = {
 SUPPORTED_ARCHS = {"llama", "qwen2", "qwen2moe", "qwen3", "qwen3moe", "phi3", "granite",
                    "internlm2", "xverse", "ernie4_5", "exaone", "seed_oss", "minicpm", "granitemoe", "smollm3",
                    "starcoder2", "falcon", "olmo", "orion", "command-r", "gptneox", "stablelm", "nemotron", "arcee",
-                   "gpt2", "starcoder", "codeshell", "qwen", "baichuan", "olmo2", "glm4", "mistral3", "pangu-embedded", "chatglm", "plamo", "deepseek", "bailingmoe"}
+                   "gpt2", "starcoder", "codeshell", "qwen", "baichuan", "olmo2", "glm4", "mistral3", "pangu-embedded", "chatglm", "plamo", "deepseek", "bailingmoe", "qwen2vl", "qwen3vl"}
 ROPE_NORM_ARCHS = {"llama", "granite", "granitemoe", "minicpm", "internlm2", "xverse", "ernie4_5", "smollm3", "olmo", "command-r", "arcee", "baichuan", "glm4", "mistral3", "chatglm", "deepseek", "bailingmoe"}     # llama_model_rope_type
 # LayerNorm families and what differs beyond the norm (llama.cpp/src/models/{starcoder2,falcon,olmo,orion,command-r}.cpp):
 #   starcoder2: biases on every matrix, non-gated GELU MLP;  falcon: fused QKV, GELU MLP, attention and MLP in parallel from the same
@@ -340,8 +345,8 @@ def config_from_gguf(meta: dict[str, Any], tensors: dict | None = None) -> Model
         n_ff_shared=int(g("expert_shared_feed_forward_length", 0) or 0) or (int(g("expert_shared_count", 0) or 0) * int(g("expert_feed_forward_length", 0) or 0)),
         n_layer_dense_lead=int(g("leading_dense_block_count", 0) or 0), expert_weights_scale=float(g("expert_weights_scale", 1.0) or 1.0),
         n_ff_dense=int(g("feed_forward_length")) if int(g("leading_dense_block_count", 0) or 0) > 0 else 0,
-        qkv_bias=arch in ("qwen2", "qwen2moe") or (tensors is not None and ("blk.0.attn_q.bias" in tensors or "blk.0.attn_qkv.bias" in tensors)),
-        qk_norm=arch in ("qwen3", "qwen3moe") or (arch != "olmo2" and tensors is not None and "blk.0.attn_q_norm.weight" in tensors),
+        qkv_bias=arch in ("qwen2", "qwen2moe", "qwen2vl") or (tensors is not None and ("blk.0.attn_q.bias" in tensors or "blk.0.attn_qkv.bias" in tensors)),
+        qk_norm=arch in ("qwen3", "qwen3moe", "qwen3vl") or (arch != "olmo2" and tensors is not None and "blk.0.attn_q_norm.weight" in tensors),
         fused_qkv=arch == "phi3" or (tensors is not None and "blk.0.attn_qkv.weight" in tensors),
         n_expert=int(g("expert_count", 0) or 0), n_expert_used=int(g("expert_used_count", 0) or 0),
         bos_id=int(meta.get("tokenizer.ggml.bos_token_id", 1)), eos_id=int(meta.get("tokenizer.ggml.eos_token_id", 2)),
