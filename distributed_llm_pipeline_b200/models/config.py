@@ -225,6 +225,8 @@ PRESETS: dict[str, ModelConfig] = {
                                 n_ctx_train=512, rope_theta=10000.0, rope_dim=64, rope_neox=True, qkv_bias=True),
     "tiny-qwen3vl": ModelConfig(name="tiny-qwen3vl", arch="qwen3vl", vocab_size=512, n_embd=256, n_layer=2, n_head=4, n_head_kv=2, head_dim=64, n_ff=512,
                                 n_ctx_train=512, rope_theta=10000.0, rope_dim=64, rope_neox=True, qk_norm=True),
+    "tiny-exaone4": ModelConfig(name="tiny-exaone4", arch="exaone4", vocab_size=512, n_embd=256, n_layer=2, n_head=4, n_head_kv=2, head_dim=64, n_ff=512,
+                                n_ctx_train=512, rope_theta=10000.0, rope_dim=64, rope_neox=True, qk_norm=True, post_norm=True, pre_norm=False),
     "tiny-command-r": ModelConfig(name="tiny-command-r", arch="command-r", vocab_size=512, n_embd=256, n_layer=2, n_head=4, n_head_kv=2,
                                   head_dim=64, n_ff=512, n_ctx_train=512, rope_theta=10000.0, rope_dim=64, norm_type="layer",
                                   parallel_residual=True, logit_scale=16.0, tie_embeddings=True),
@@ -264,7 +266,7 @@ PRESETS: dict[str, ModelConfig] = {
 SUPPORTED_ARCHS = {"llama", "qwen2", "qwen2moe", "qwen3", "qwen3moe", "phi3", "granite",
                    "internlm2", "xverse", "ernie4_5", "exaone", "seed_oss", "minicpm", "granitemoe", "smollm3",
                    "starcoder2", "falcon", "olmo", "orion", "command-r", "gptneox", "stablelm", "nemotron", "arcee",
-                   "gpt2", "starcoder", "codeshell", "qwen", "baichuan", "olmo2", "glm4", "mistral3", "pangu-embedded", "chatglm", "plamo", "deepseek", "bailingmoe", "qwen2vl", "qwen3vl"}
+                   "gpt2", "starcoder", "codeshell", "qwen", "baichuan", "olmo2", "glm4", "mistral3", "pangu-embedded", "chatglm", "plamo", "deepseek", "bailingmoe", "qwen2vl", "qwen3vl", "exaone4"}
 ROPE_NORM_ARCHS = {"llama", "granite", "granitemoe", "minicpm", "internlm2", "xverse", "ernie4_5", "smollm3", "olmo", "command-r", "arcee", "baichuan", "glm4", "mistral3", "chatglm", "deepseek", "bailingmoe"}     # llama_model_rope_type
 # LayerNorm families and what differs beyond the norm (llama.cpp/src/models/{starcoder2,falcon,olmo,orion,command-r}.cpp):
 #   starcoder2: biases on every matrix, non-gated GELU MLP;  falcon: fused QKV, GELU MLP, attention and MLP in parallel from the same
@@ -317,6 +319,8 @@ def config_from_gguf(meta: dict[str, Any], tensors: dict | None = None) -> Model
                     yarn_beta_fast=float(g("rope.scaling.yarn_beta_fast", 32.0)), yarn_beta_slow=float(g("rope.scaling.yarn_beta_slow", 1.0)))
     tie = tensors is not None and "output.weight" not in tensors
     n_layer = int(g("block_count"))
+    if arch == "exaone4" and (n_layer == 64 or int(g("attention.sliding_window", 0) or 0) > 0):
+        raise NotImplementedError("exaone4 checkpoints with sliding-window layers (the 32B model) are not supported")
     if arch == "mistral3" and float(g("attention.temperature_scale", 0.0) or 0.0) != 0.0:
         raise NotImplementedError("mistral3 checkpoints with a position-dependent attention temperature are not supported")
     if tensors is not None and "blk.0.ffn_down.weight" in tensors and int(g("feed_forward_length")) // (2 if arch == "qwen" else 1) != tensors["blk.0.ffn_down.weight"].shape[-1]:
@@ -334,7 +338,7 @@ def config_from_gguf(meta: dict[str, Any], tensors: dict | None = None) -> Model
         rms_eps=float(g("attention.layer_norm_epsilon", 1e-5) if arch in LAYERNORM_ARCHS else g("attention.layer_norm_rms_epsilon", 1e-5)),
         norm_type="layer" if arch in LAYERNORM_ARCHS else "rms", ffn_act="gelu" if arch in ("starcoder2", "falcon", "gptneox", "gpt2", "starcoder", "codeshell") else "relu2" if arch in ("nemotron", "arcee") else "swiglu",
         attn_out_bias=tensors is not None and "blk.0.attn_output.bias" in tensors and arch not in LAYERNORM_ARCHS,
-        post_norm=arch in ("olmo2", "glm4"), pre_norm=arch != "olmo2", qk_norm_full=arch == "olmo2",
+        post_norm=arch in ("olmo2", "glm4", "exaone4"), pre_norm=arch not in ("olmo2", "exaone4"), qk_norm_full=arch == "olmo2",
         parallel_residual=arch in ("falcon", "command-r", "plamo") or (arch == "gptneox" and bool(g("use_parallel_residual", True)))
         or (arch == "stablelm" and tensors is not None and "blk.0.ffn_norm.weight" not in tensors), fused_gate_up=arch in ("phi3", "glm4", "chatglm"), rope_theta=float(g("rope.freq_base", 10000.0)),
         rope_dim=int(g("rope.dimension_count", head_dim)), rope_neox=arch not in ROPE_NORM_ARCHS, rope_scale_linear=scale,
