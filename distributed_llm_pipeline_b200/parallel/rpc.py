@@ -219,6 +219,28 @@ class RpcEngine:
             w.close()
 
 
+def free_port_run(n: int = 2, host: str = "127.0.0.1") -> int:
+    """First port of a run of `n` consecutive ports that are free right now (the local launchers number their workers base, base+1, ...)."""
+    for _ in range(200):
+        probe = socket.socket()
+        probe.bind((host, 0))
+        base = probe.getsockname()[1]
+        probe.close()
+        socks = []
+        try:
+            for i in range(n):
+                s = socket.socket()
+                socks.append(s)
+                s.bind((host, base + i))
+            return base
+        except OSError:
+            continue
+        finally:
+            for s in socks:
+                s.close()
+    raise WorkerError(f"no run of {n} free ports on {host}")
+
+
 def launch_local_workers(model: str, n_workers: int, base_port: int = 50052, n_ctx: int = 2048, n_layer: int | None = None,
                          threads: int | None = None, verbose: bool = False, sanitize: str | None = None,
                          stderr=None) -> tuple[list[subprocess.Popen], list[str]]:

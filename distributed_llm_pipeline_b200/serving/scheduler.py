@@ -83,6 +83,7 @@ class Slot:
     decoder: StreamDecoder | None = None
     next_token: int = 0
     t_last_used: float = 0.0
+    last_req: Request | None = None     # the slot's latest request, kept after it ends (GET /slots shows its parameters)
 
 
 class Metrics:
@@ -229,7 +230,7 @@ class Scheduler:
         eng.truncate_seq(slot.sid, keep)
         slot.cache_tokens = slot.cache_tokens[:keep]
         slot.n_past = keep
-        slot.req, slot.state = req, SlotState.PROMPT
+        slot.req, slot.last_req, slot.state = req, req, SlotState.PROMPT
         slot.sampler = Sampler(req.sampling, self.tok)
         slot.sampler.history = list(req.prompt_ids)      # penalties and DRY look back over the prompt too (server-context.cpp: prompt tokens
         #                                                  are accepted into the sampler without advancing the grammar)
@@ -294,11 +295,13 @@ class Scheduler:
             s.n_past += len(chunk)
             s.cache_tokens.extend(chunk)
             req.n_prompt_processed += len(chunk)
-            self.metrics.add(prompt_tokens_total=len(chunk), n_tokens_max=0)
-            self.metrics.c["n_tokens_max"] = max(self.metrics.c["n_tokens_max"], len(chunk))
+            # counters as server-context.cpp:523-547 keeps them: every forward is a decode, n_tokens_max is the longest slot context,
+            # and the token sampled from the prompt's last logits is a predicted token
+            self.metrics.add(prompt_tokens_total=len(chunk), n_decode_total=1, n_busy_slots_total=1)
+            self.metrics.c["n_tokens_max"] = max(self.metrics.c["n_tokens_max"], s.n_past)
             if s.n_past == len(req.prompt_ids):  # prompt complete: sample the first token from its logits
                 tok = self._sample_rows(logits[None], [s])[0]
-                self.metrics.add(prompt_seconds_total=time.time() - req.t_start)
+                self.metrics.add(prompt_seconds_total=time.time() - req.t_start, tokens_predicted_total=1)
                 req.t_first_token = time.time()
                 s.state = SlotState.GENERATING
                 self._accept(s, tok)
@@ -341,6 +344,7 @@ class Scheduler:
                 for s, t in zip(gen, new):
                     s.cache_tokens.append(s.next_token)
                     s.n_past += 1
+                    self.metrics.c["n_tokens_max"] = max(self.metrics.c["n_tokens_max"], s.n_past)
                     self._accept(s, int(t))
         return True
 
@@ -595,5 +599,22 @@ class Scheduler:
         return self.run_on_engine(job)
 
     def slots_info(self) -> list[dict]:
-        return [{"id": s.idx, "state": s.state.name.lower(), "n_past": s.n_past, "n_cached": len(s.cache_tokens),
-                 "request": s.req.id if s.req else None} for s in self.slots]
+        """GET /slots.  The reference's fields (`server_slot::to_json`, server-context.cpp:360-420: id, n_ctx, speculative, is_processing and,
+        once the slot has served a task, id_task / params / next_token) plus this scheduler's own (state, n_past, n_cached, request)."""
+        from dataclasses import asdict
+        out = []
+        for s in self.slots:
+            d = {"id": s.idx, "n_ctx": self.eng.n_ctx, "speculative": self.draft_eng is not None, "is_processing": s.state != SlotState.IDLE,
+                 "state": s.state.name.lower(), "n_past": s.n_past, "n_cached": len(s.cache_tokens), "request": s.req.id if s.req else None}
+            r = s.last_req
+            if r is not None:
+                sp = {k: v for k, v in asdict(r.sampling).items() if k not in ("logit_bias", "dry_breakers", "json_schema", "grammar_trigger_words",
+                                                                                "grammar_trigger_patterns")}
+                sp.update(max_tokens=r.n_predict, n_predict=r.n_predict, n_keep=r.n_keep, ignore_eos=r.ignore_eos, n_probs=r.n_probs,
+                          stream=False, lora=[])
+                sp["speculative.n_max"] = r.n_draft or self.n_draft_default
+                d.update(id_task=r.id, params=sp,
+                         next_token=[{"has_next_token": r.finish_reason is None, "has_new_line": "\n" in r.text,
+                                      "n_remain": max(0, r.n_predict - len(r.output_ids)), "n_decoded": len(r.output_ids)}])
+            out.append(d)
+        return out

@@ -6,7 +6,7 @@ import pytest
 import torch
 
 from distributed_llm_pipeline_b200.models.reference import ReferenceModel, nmse
-from distributed_llm_pipeline_b200.parallel.rpc import RpcEngine, WorkerClient, WorkerError, launch_local_workers
+from distributed_llm_pipeline_b200.parallel.rpc import RpcEngine, WorkerClient, WorkerError, free_port_run, launch_local_workers
 from distributed_llm_pipeline_b200.serving.sampler import SamplingParams
 from distributed_llm_pipeline_b200.serving.scheduler import Scheduler
 from distributed_llm_pipeline_b200.utils.tokenizer import Tokenizer
@@ -22,10 +22,14 @@ def _free_ports(n):
     return ports
 
 
+def _free_base(n=2):
+    return free_port_run(n)
+
+
 @pytest.fixture(scope="module", params=["Q8_0", "Q4_K_M"])
 def chain(request, tmp_models):
     path = tmp_models[("tiny", request.param)]
-    base = _free_ports(1)[0]
+    base = _free_base(2)
     procs, eps = launch_local_workers(path, 2, base_port=base, n_ctx=128, threads=2)
     eng = RpcEngine(eps, max_seqs=2)
     yield path, eng, eps
@@ -83,7 +87,7 @@ def test_worker_crash_is_healed_by_reconnect_and_replay(tmp_models):
     import signal
     from distributed_llm_pipeline_b200.parallel.rpc import LocalWorkerPool
     path = tmp_models[("tiny", "Q8_0")]
-    pool = LocalWorkerPool(path, 2, base_port=_free_ports(1)[0], n_ctx=128, threads=2)
+    pool = LocalWorkerPool(path, 2, base_port=_free_base(2), n_ctx=128, threads=2)
     try:
         eng = RpcEngine(pool.endpoints, max_seqs=2, recover=True, recover_wait_s=30)
         prompt = [1, 5, 9, 200, 33, 7, 8]
@@ -120,7 +124,7 @@ def test_other_architectures_on_cpu_workers(tmp_models, key):
     """qwen2 (bias), qwen3 (per-head Q/K norm), phi3 (fused tensors), granite / minicpm (four scalars), seed_oss (its own norm tensor name),
     qwen (fused QKV with bias, separate gate / up), exaone, internlm2 - through two native stage workers."""
     path = tmp_models[key]
-    procs, eps = launch_local_workers(path, 2, base_port=_free_ports(1)[0], n_ctx=64, threads=2)
+    procs, eps = launch_local_workers(path, 2, base_port=_free_base(2), n_ctx=64, threads=2)
     try:
         eng = RpcEngine(eps, max_seqs=1)
         ref = ReferenceModel.from_gguf(path)
@@ -152,7 +156,7 @@ def test_q8_0_avx2_and_vnni_kernels(tmp_models, monkeypatch):
     for no_vnni in (False, True):
         if no_vnni:
             monkeypatch.setenv("DLP_WORKER_NO_VNNI", "1")
-        procs, eps = launch_local_workers(path, 2, base_port=_free_ports(1)[0], n_ctx=64, threads=2)
+        procs, eps = launch_local_workers(path, 2, base_port=_free_base(2), n_ctx=64, threads=2)
         try:
             eng = RpcEngine(eps, max_seqs=1)
             sid = eng.alloc_seq()

@@ -10,7 +10,7 @@ import time
 
 import pytest
 
-from distributed_llm_pipeline_b200.parallel.rpc import RpcEngine, launch_local_workers
+from distributed_llm_pipeline_b200.parallel.rpc import RpcEngine, free_port_run, launch_local_workers
 from distributed_llm_pipeline_b200.runtime import native
 
 REPO = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
@@ -33,7 +33,7 @@ def test_worker_under_sanitizer(tmp_models, tmp_path, kind):
         pytest.skip(f"sanitizer runtime not available: {str(e)[:200]}")
     log = open(tmp_path / f"worker-{kind}.log", "w+")
     os.environ.setdefault("ASAN_OPTIONS", "detect_leaks=1")
-    procs, eps = launch_local_workers(tmp_models[("tiny", "Q8_0")], 2, base_port=_free_port(), n_ctx=64, threads=2, sanitize=kind, stderr=log)
+    procs, eps = launch_local_workers(tmp_models[("tiny", "Q8_0")], 2, base_port=free_port_run(2), n_ctx=64, threads=2, sanitize=kind, stderr=log)
     try:
         eng = RpcEngine(eps, max_seqs=2)
         a, b = eng.alloc_seq(), eng.alloc_seq()

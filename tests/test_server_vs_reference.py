@@ -46,7 +46,7 @@ def pair(tmp_models, tmp_path_factory):
     env = ref_build.cpu_env(str(tmp_path_factory.mktemp("refsrv")))
     rp = _free_port()
     proc = subprocess.Popen([ref_build.exe("llama-server"), "-m", model, "-ngl", "0", "-c", "512", "-np", "2", "--host", "127.0.0.1", "--port", str(rp), "-t", "4",
-                             "--no-warmup"], env=env, stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL)
+                             "--no-warmup", "--metrics", "--slots"], env=env, stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL)
     for _ in range(200):
         try:
             _get(rp, "/health")
@@ -343,3 +343,40 @@ def test_context_shift_keeps_generating_like_the_reference(tmp_models, tmp_path)
         sched.stop()
         proc.terminate()
         proc.wait()
+
+
+def test_zz_metrics_and_slots_agree(pair):
+    """Runs last on the shared pair: both servers have then served the same requests, so the Prometheus names must be the same set (ours adds
+    the two KV-pool gauges) and the counters that do not depend on wall time must be equal after one more identical request on each side."""
+    ours, ref = pair
+
+    def metrics(port):
+        text = urllib.request.urlopen(f"http://127.0.0.1:{port}/metrics", timeout=30).read().decode()
+        vals = {ln.split()[0]: float(ln.split()[1]) for ln in text.splitlines() if ln and not ln.startswith("#")}
+        kinds = {ln.split()[2]: ln.split()[3] for ln in text.splitlines() if ln.startswith("# TYPE")}
+        return vals, kinds
+
+    before = {p: metrics(p)[0] for p in (ours, ref)}
+    body = {"prompt": "one two three four five six", "n_predict": 5, "temperature": 0, "cache_prompt": False, "logit_bias": [[7, 100]]}
+    for p in (ours, ref):
+        _post(p, "/completion", body)
+    (va, ka), (vb, kb) = metrics(ours), metrics(ref)
+    assert set(vb) <= set(va) and set(va) - set(vb) == {"llamacpp:kv_cache_pages_free", "llamacpp:kv_cache_pages_total"}
+    assert all(ka[k] == kb[k] for k in kb)
+    for name in ("prompt_tokens_total", "tokens_predicted_total", "n_decode_total"):
+        k = "llamacpp:" + name
+        assert va[k] - before[ours][k] == vb[k] - before[ref][k] > 0, name
+    assert va["llamacpp:requests_processing"] == vb["llamacpp:requests_processing"] == 0
+    sa, sb = _get(ours, "/slots"), _get(ref, "/slots")
+    assert len(sa) == len(sb) == 2
+    served_a, served_b = [x for x in sa if "params" in x], [x for x in sb if "params" in x]
+    assert served_a and served_b
+    for x in sa + sb:
+        assert {"id", "n_ctx", "speculative", "is_processing"} <= set(x) and x["is_processing"] is False
+    # the parameter record of a served slot carries the reference's sampling fields under the same names
+    shared = set(served_a[0]["params"]) & set(served_b[0]["params"])
+    assert {"temperature", "top_k", "top_p", "min_p", "typical_p", "repeat_last_n", "repeat_penalty", "presence_penalty", "frequency_penalty",
+            "dry_multiplier", "dry_base", "dry_allowed_length", "mirostat", "mirostat_tau", "mirostat_eta", "xtc_probability", "xtc_threshold",
+            "top_n_sigma", "dynatemp_range", "dynatemp_exponent", "n_predict", "max_tokens", "n_keep", "ignore_eos", "n_probs", "stream", "lora",
+            "speculative.n_max"} <= shared
+    assert set(served_a[0]["next_token"][0]) == set(served_b[0]["next_token"][0])
