@@ -62,13 +62,20 @@ class GGMLType(enum.IntEnum):
     Q5_K = 13
     Q6_K = 14
     Q8_K = 15
+    IQ2_XXS = 16
+    IQ2_XS = 17
+    IQ3_XXS = 18
+    IQ1_S = 19
     IQ4_NL = 20
+    IQ3_S = 21
+    IQ2_S = 22
     IQ4_XS = 23
     I8 = 24
     I16 = 25
     I32 = 26
     I64 = 27
     F64 = 28
+    IQ1_M = 29
     BF16 = 30
     TQ1_0 = 34
     TQ2_0 = 35
@@ -104,6 +111,13 @@ BLOCK_GEOMETRY = {
     GGMLType.TQ1_0: (256, 48 + 4 + 2),
     GGMLType.TQ2_0: (256, 64 + 2),
     GGMLType.MXFP4: (32, 1 + 16),
+    GGMLType.IQ2_XXS: (256, 2 + 64),
+    GGMLType.IQ2_XS: (256, 2 + 64 + 8),
+    GGMLType.IQ2_S: (256, 2 + 64 + 8 + 8),
+    GGMLType.IQ3_XXS: (256, 2 + 96),
+    GGMLType.IQ3_S: (256, 2 + 64 + 8 + 32 + 4),
+    GGMLType.IQ1_S: (256, 2 + 32 + 16),
+    GGMLType.IQ1_M: (256, 32 + 16 + 8),
 }
 
 

