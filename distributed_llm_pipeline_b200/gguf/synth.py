@@ -130,7 +130,7 @@ def _tensor_plan(cfg: ModelConfig, rope_freqs: bool):
     """(name, shape, layer, init_std) for every tensor of the architecture; shapes row-major [out, in]."""
     E, F = cfg.n_embd, cfg.n_ff
     nl = norm_layout(cfg)
-    all_bias = cfg.arch in ("starcoder2", "gptneox", "gpt2", "starcoder", "codeshell")       # biases on the attention output and the MLP as well
+    all_bias = cfg.arch in ("starcoder2", "gptneox", "gpt2", "starcoder", "codeshell", "phi2")       # biases on the attention output and the MLP as well
 
     def norm(name, il, kind):
         return ([(name + ".weight", (E,), il, 0.0)] if "w" in kind else []) + ([(name + ".bias", (E,), il, 0.05)] if "b" in kind else [])
@@ -200,6 +200,8 @@ def _tensor_plan(cfg: ModelConfig, rope_freqs: bool):
     plan += norm("output_norm", -1, nl["out"])
     if not cfg.tie_embeddings:
         plan.append(("output.weight", (cfg.vocab_size, E), -1, 0.02))
+    if cfg.arch == "phi2":
+        plan.append(("output.bias", (cfg.vocab_size,), -1, 0.05))
     return plan
 
 
@@ -245,9 +247,9 @@ def write_synthetic_gguf(path: str, cfg: ModelConfig, ftype: str = "F16", seed: 
         w.add(f"{a}.rope.scaling.factor", float(1.0 / cfg.rope_scale_linear), ValueType.FLOAT32)
     if a == "gptneox":
         w.add(f"{a}.use_parallel_residual", bool(cfg.parallel_residual))
-    if a == "qwen3vl":
+    if a in ("qwen3vl", "qwen3vlmoe"):
         w.add(f"{a}.n_deepstack_layers", 0, ValueType.UINT32)
-    if a in ("qwen2vl", "qwen3vl"):      # temporal / height / width / extra shares of the rotary pairs (text tokens use one position for all of them)
+    if a in ("qwen2vl", "qwen3vl", "qwen3vlmoe"):      # temporal / height / width / extra shares of the rotary pairs (text tokens use one position for all of them)
         q = cfg.rope_dim // 8
         w.add(f"{a}.rope.dimension_sections", np.asarray([q, (cfg.rope_dim // 2 - q) // 2, cfg.rope_dim // 2 - q - (cfg.rope_dim // 2 - q) // 2, 0], np.int32), etype=ValueType.INT32)
     if cfg.is_moe:

@@ -71,7 +71,8 @@ class ModelConfig:
     @property
     def generic(self) -> bool:
         """True for families that run the unfused layer path (models/llama.py `_layer_generic`)."""
-        return self.norm_type != "rms" or self.ffn_act != "swiglu" or self.parallel_residual or self.post_norm or not self.pre_norm or self.attn_out_bias
+        return (self.norm_type != "rms" or self.ffn_act != "swiglu" or self.parallel_residual or self.post_norm or not self.pre_norm or self.attn_out_bias
+                or self.qk_norm_full)
 
     # smollm3: every `no_rope_step`-th layer attends without rotary position encoding (`llama.cpp/src/models/smollm3.cpp:26`)
     no_rope_step: int = 0
@@ -183,6 +184,9 @@ PRESETS: dict[str, ModelConfig] = {
     "tiny-gptneox": ModelConfig(name="tiny-gptneox", arch="gptneox", vocab_size=512, n_embd=256, n_layer=2, n_head=4, n_head_kv=4,
                                 head_dim=64, n_ff=1024, n_ctx_train=512, rope_theta=10000.0, rope_dim=16, rope_neox=True, fused_qkv=True, qkv_bias=True,
                                 norm_type="layer", ffn_act="gelu", parallel_residual=True),
+    "tiny-phi2": ModelConfig(name="tiny-phi2", arch="phi2", vocab_size=512, n_embd=256, n_layer=2, n_head=4, n_head_kv=4,
+                             head_dim=64, n_ff=1024, n_ctx_train=512, rope_theta=10000.0, rope_dim=32, rope_neox=True, fused_qkv=True, qkv_bias=True,
+                             norm_type="layer", ffn_act="gelu", parallel_residual=True),
     "tiny-stablelm": ModelConfig(name="tiny-stablelm", arch="stablelm", vocab_size=512, n_embd=256, n_layer=2, n_head=4, n_head_kv=2,
                                  head_dim=64, n_ff=512, n_ctx_train=512, rope_theta=10000.0, rope_dim=32, rope_neox=True, norm_type="layer"),
     "tiny-nemotron": ModelConfig(name="tiny-nemotron", arch="nemotron", vocab_size=512, n_embd=256, n_layer=2, n_head=4, n_head_kv=2,
@@ -225,6 +229,11 @@ PRESETS: dict[str, ModelConfig] = {
                                 n_ctx_train=512, rope_theta=10000.0, rope_dim=64, rope_neox=True, qkv_bias=True),
     "tiny-qwen3vl": ModelConfig(name="tiny-qwen3vl", arch="qwen3vl", vocab_size=512, n_embd=256, n_layer=2, n_head=4, n_head_kv=2, head_dim=64, n_ff=512,
                                 n_ctx_train=512, rope_theta=10000.0, rope_dim=64, rope_neox=True, qk_norm=True),
+    "tiny-qwen3vlmoe": ModelConfig(name="tiny-qwen3vlmoe", arch="qwen3vlmoe", vocab_size=512, n_embd=256, n_layer=2, n_head=4, n_head_kv=2, head_dim=64,
+                                   n_ff=256, n_ctx_train=512, rope_theta=10000.0, rope_dim=64, rope_neox=True, qk_norm=True, n_expert=4, n_expert_used=2),
+    "tiny-olmoe": ModelConfig(name="tiny-olmoe", arch="olmoe", vocab_size=512, n_embd=256, n_layer=2, n_head=4, n_head_kv=4, head_dim=64, n_ff=256,
+                              n_ctx_train=512, rope_theta=10000.0, rope_dim=64, rope_neox=True, qk_norm_full=True, n_expert=4, n_expert_used=2,
+                              moe_norm_topk=False),
     "tiny-exaone4": ModelConfig(name="tiny-exaone4", arch="exaone4", vocab_size=512, n_embd=256, n_layer=2, n_head=4, n_head_kv=2, head_dim=64, n_ff=512,
                                 n_ctx_train=512, rope_theta=10000.0, rope_dim=64, rope_neox=True, qk_norm=True, post_norm=True, pre_norm=False),
     "tiny-command-r": ModelConfig(name="tiny-command-r", arch="command-r", vocab_size=512, n_embd=256, n_layer=2, n_head=4, n_head_kv=2,
@@ -266,7 +275,7 @@ PRESETS: dict[str, ModelConfig] = {
 SUPPORTED_ARCHS = {"llama", "qwen2", "qwen2moe", "qwen3", "qwen3moe", "phi3", "granite",
                    "internlm2", "xverse", "ernie4_5", "exaone", "seed_oss", "minicpm", "granitemoe", "smollm3",
                    "starcoder2", "falcon", "olmo", "orion", "command-r", "gptneox", "stablelm", "nemotron", "arcee",
-                   "gpt2", "starcoder", "codeshell", "qwen", "baichuan", "olmo2", "glm4", "mistral3", "pangu-embedded", "chatglm", "plamo", "deepseek", "bailingmoe", "qwen2vl", "qwen3vl", "exaone4"}
+                   "gpt2", "starcoder", "codeshell", "qwen", "baichuan", "olmo2", "glm4", "mistral3", "pangu-embedded", "chatglm", "plamo", "deepseek", "bailingmoe", "qwen2vl", "qwen3vl", "exaone4", "phi2", "olmoe", "qwen3vlmoe"}
 ROPE_NORM_ARCHS = {"llama", "granite", "granitemoe", "minicpm", "internlm2", "xverse", "ernie4_5", "smollm3", "olmo", "command-r", "arcee", "baichuan", "glm4", "mistral3", "chatglm", "deepseek", "bailingmoe"}     # llama_model_rope_type
 # LayerNorm families and what differs beyond the norm (llama.cpp/src/models/{starcoder2,falcon,olmo,orion,command-r}.cpp):
 #   starcoder2: biases on every matrix, non-gated GELU MLP;  falcon: fused QKV, GELU MLP, attention and MLP in parallel from the same
@@ -276,7 +285,8 @@ ROPE_NORM_ARCHS = {"llama", "granite", "granitemoe", "minicpm", "internlm2", "xv
 #   nemotron: rotary on part of each head, non-gated ReLU^2 MLP;   arcee keeps RMSNorm but has the same non-gated ReLU^2 MLP
 #   gpt2, starcoder (v1): learned position embeddings instead of rotary (starcoder: multi-query), fused QKV, biases everywhere, GELU MLP
 #   codeshell: the same block with rotary.   (qwen v1 and baichuan-7B are RMSNorm / SwiGLU graphs and run the fused path.)
-LAYERNORM_ARCHS = {"starcoder2", "falcon", "olmo", "orion", "command-r", "gptneox", "stablelm", "nemotron", "gpt2", "starcoder", "codeshell"}
+#   phi2: one LayerNorm feeds attention and MLP in parallel, fused QKV, biases everywhere including the output matrix, rotary on part of each head
+LAYERNORM_ARCHS = {"starcoder2", "falcon", "olmo", "orion", "command-r", "gptneox", "stablelm", "nemotron", "gpt2", "starcoder", "codeshell", "phi2"}
 LEARNED_POS_ARCHS = {"gpt2", "starcoder"}
 
 
@@ -336,21 +346,21 @@ def config_from_gguf(meta: dict[str, Any], tensors: dict | None = None) -> Model
         else int(g("feed_forward_length")) // (2 if arch == "qwen" else 1),      # qwen v1 files store twice the MLP width (llama-model.cpp: n_ff/2)
         n_ctx_train=int(g("context_length", 2048)),
         rms_eps=float(g("attention.layer_norm_epsilon", 1e-5) if arch in LAYERNORM_ARCHS else g("attention.layer_norm_rms_epsilon", 1e-5)),
-        norm_type="layer" if arch in LAYERNORM_ARCHS else "rms", ffn_act="gelu" if arch in ("starcoder2", "falcon", "gptneox", "gpt2", "starcoder", "codeshell") else "relu2" if arch in ("nemotron", "arcee") else "swiglu",
+        norm_type="layer" if arch in LAYERNORM_ARCHS else "rms", ffn_act="gelu" if arch in ("starcoder2", "falcon", "gptneox", "gpt2", "starcoder", "codeshell", "phi2") else "relu2" if arch in ("nemotron", "arcee") else "swiglu",
         attn_out_bias=tensors is not None and "blk.0.attn_output.bias" in tensors and arch not in LAYERNORM_ARCHS,
-        post_norm=arch in ("olmo2", "glm4", "exaone4"), pre_norm=arch not in ("olmo2", "exaone4"), qk_norm_full=arch == "olmo2",
-        parallel_residual=arch in ("falcon", "command-r", "plamo") or (arch == "gptneox" and bool(g("use_parallel_residual", True)))
+        post_norm=arch in ("olmo2", "glm4", "exaone4"), pre_norm=arch not in ("olmo2", "exaone4"), qk_norm_full=arch in ("olmo2", "olmoe"),
+        parallel_residual=arch in ("falcon", "command-r", "plamo", "phi2") or (arch == "gptneox" and bool(g("use_parallel_residual", True)))
         or (arch == "stablelm" and tensors is not None and "blk.0.ffn_norm.weight" not in tensors), fused_gate_up=arch in ("phi3", "glm4", "chatglm"), rope_theta=float(g("rope.freq_base", 10000.0)),
         rope_dim=int(g("rope.dimension_count", head_dim)), rope_neox=arch not in ROPE_NORM_ARCHS, rope_scale_linear=scale,
         embedding_scale=float(g("embedding_scale") or dflt["embedding_scale"]), residual_scale=float(g("residual_scale") or dflt["residual_scale"]),
         logit_scale=(1.0 / float(g("logit_scale") or 1.0)) if arch == "command-r" else float(g("logit_scale") or dflt["logit_scale"]), attention_scale=float(g("attention.scale", 0.0) or 0.0),
         no_rope_step=4 if arch == "smollm3" else 1 if arch in LEARNED_POS_ARCHS else 0, learned_pos=arch in LEARNED_POS_ARCHS,
-        moe_norm_topk=bool(g("expert_weights_norm", False)) if arch == "bailingmoe" else arch not in ("qwen2moe", "deepseek"),
+        moe_norm_topk=bool(g("expert_weights_norm", False)) if arch == "bailingmoe" else arch not in ("qwen2moe", "deepseek", "olmoe"),
         n_ff_shared=int(g("expert_shared_feed_forward_length", 0) or 0) or (int(g("expert_shared_count", 0) or 0) * int(g("expert_feed_forward_length", 0) or 0)),
         n_layer_dense_lead=int(g("leading_dense_block_count", 0) or 0), expert_weights_scale=float(g("expert_weights_scale", 1.0) or 1.0),
         n_ff_dense=int(g("feed_forward_length")) if int(g("leading_dense_block_count", 0) or 0) > 0 else 0,
         qkv_bias=arch in ("qwen2", "qwen2moe", "qwen2vl") or (tensors is not None and ("blk.0.attn_q.bias" in tensors or "blk.0.attn_qkv.bias" in tensors)),
-        qk_norm=arch in ("qwen3", "qwen3moe", "qwen3vl") or (arch != "olmo2" and tensors is not None and "blk.0.attn_q_norm.weight" in tensors),
+        qk_norm=arch in ("qwen3", "qwen3moe", "qwen3vl", "qwen3vlmoe") or (arch not in ("olmo2", "olmoe") and tensors is not None and "blk.0.attn_q_norm.weight" in tensors),
         fused_qkv=arch == "phi3" or (tensors is not None and "blk.0.attn_qkv.weight" in tensors),
         n_expert=int(g("expert_count", 0) or 0), n_expert_used=int(g("expert_used_count", 0) or 0),
         bos_id=int(meta.get("tokenizer.ggml.bos_token_id", 1)), eos_id=int(meta.get("tokenizer.ggml.eos_token_id", 2)),

@@ -101,6 +101,8 @@ class LlamaEngine:
         self.max_tokens = max(max_batch_tokens, max_seqs)
         self.Hq, self.Hkv, self.D = weights.n_head_local, weights.n_head_kv_local, cfg.head_dim
         self.E, self.F = cfg.n_embd, weights.n_ff_local
+        if dev.type == "cuda" and self.D not in (64, 128):
+            raise NotImplementedError(f"head dimension {self.D}: the attention kernels are built for 64 and 128 (phi-2 has 80, gemma 256)")
         max_pages = (n_ctx + page_size - 1) // page_size
         if n_pages is None:
             n_pages = max_pages * max_seqs
@@ -120,8 +122,8 @@ class LlamaEngine:
         self.fused_tp = bool(getattr(self.comm, "fused", False)) and self.comm.tp_size > 1 and not cfg.is_moe
         if cfg.generic and self.fused_tp:
             raise NotImplementedError(f"the {cfg.arch} family runs the generic layer path: tensor parallelism through --tp-impl nccl")
-        if cfg.generic and cfg.is_moe:
-            raise NotImplementedError("routed experts are not implemented on the generic layer path")
+        if cfg.generic and cfg.is_moe and (cfg.norm_type != "rms" or cfg.parallel_residual or cfg.post_norm or not cfg.pre_norm):
+            raise NotImplementedError("routed experts on the generic layer path need the sequential pre-RMSNorm block form")
         self.sp_ok = False
         self._greedy_now = False
         if self.fused_tp:
@@ -398,6 +400,9 @@ class LlamaEngine:
             ffn_in = xf
         else:
             ffn_in = self._norm(h, lw.ffn_norm, lw.ffn_norm_b, delta=d, out=self.xn[:T])       # h += d inside
+        if lw.router is not None:         # olmoe: routed experts behind the same pre-norm (adds its output to h)
+            self._moe(lw, T, ffn_in)
+            return
         if cfg.ffn_act in ("gelu", "relu2"):
             up = ops.linear(lw.w_up, ffn_in, "f32", out=self.up32[:T], scratch=self._scratch_for(lw.w_up))
             act = ops.bias_act(up, lw.b_up, cfg.ffn_act, out=self.act[:T])
@@ -707,6 +712,8 @@ class LlamaEngine:
         else:
             xn = self._norm(hsel.contiguous(), self.w.out_norm, self.w.out_norm_b)
             lg = ops.linear(self.w.lm_head, xn, "f32", out=self.logits[:n], scratch=self._scratch_for(self.w.lm_head))
+        if self.w.out_b is not None:        # phi2: the output matrix has a bias
+            lg.add_(self.w.out_b)
         return self.comm.allgather_logits(lg, self.w.vocab_range, cfg.vocab_size)
 
     # ---- public: prefill ------------------------------------------------------------------------
@@ -758,6 +765,8 @@ class LlamaEngine:
                 raise ValueError("all_logits needs the tokens to fit one chunk")
             xn = self._norm(self.h[:T], self.w.out_norm, self.w.out_norm_b)
             lg = ops.linear(self.w.lm_head, xn, "f32", scratch=self._scratch_for(self.w.lm_head))
+            if self.w.out_b is not None:
+                lg.add_(self.w.out_b)
             return self.comm.allgather_logits(lg, self.w.vocab_range, self.cfg.vocab_size)
         return self._head(slice(T - 1, T), 1)[0]
 

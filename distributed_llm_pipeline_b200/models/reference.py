@@ -241,7 +241,8 @@ class ReferenceModel:
         xn = self.norm(h, "output_norm")
         if self.observer is not None:
             self.observer("output.weight" if "output.weight" in w else "token_embd.weight", xn, None)
-        return xn @ out_w.T / c.logit_scale
+        lg = xn @ out_w.T / c.logit_scale
+        return lg + w["output.bias"] if "output.bias" in w else lg      # phi2
 
     # ---- full forward ---------------------------------------------------------------------
     def forward(self, tokens, cache: RefKVCache, layers: range | None = None, hidden: torch.Tensor | None = None,

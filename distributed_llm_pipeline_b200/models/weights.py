@@ -76,6 +76,7 @@ class ModelWeights:
     n_ff_local: int = 0
     out_norm_b: torch.Tensor | None = None
     pos_embd: torch.Tensor | None = None      # fp32 [n_ctx_train, E] learned positions (gpt2, starcoder; first stage only)
+    out_b: torch.Tensor | None = None         # fp32 bias of the output matrix, rows [v0, v1) (phi2)
 
     def nbytes(self) -> int:
         tot = 0
@@ -328,4 +329,5 @@ def load_weights(src: str | GGUFModelFiles, device, layer_range: range | None = 
     freqs = f32("rope_freqs.weight") if "rope_freqs.weight" in f else None
     return ModelWeights(cfg, layers, layer_range, tp_rank, tp_size, tok, out_norm, lm, (v0, v1), freqs,
                         n_head_local=hq1 - hq0, n_head_kv_local=n_kv_local, n_ff_local=cfg.n_ff // tp_size, out_norm_b=out_norm_b,
-                        pos_embd=f32("position_embd.weight") if (cfg.learned_pos and first_stage) else None)
+                        pos_embd=f32("position_embd.weight") if (cfg.learned_pos and first_stage) else None,
+                        out_b=f32("output.bias")[v0:v1].contiguous() if (last_stage and "output.bias" in f) else None)

@@ -61,6 +61,10 @@ CASES = {
     "olmo2": ("Olmo2Config", "Olmo2ForCausalLM", {"num_key_value_heads": 2}),
     "glm4": ("Glm4Config", "Glm4ForCausalLM", {"partial_rotary_factor": 0.5, "head_dim": 64, "attention_bias": True}),
     "olmo": ("OlmoConfig", "OlmoForCausalLM", {"clip_qkv": None, "num_key_value_heads": 4}),
+    "olmoe": ("OlmoeConfig", "OlmoeForCausalLM", {"intermediate_size": 128, "num_experts": 4, "num_experts_per_tok": 2, "norm_topk_prob": False,
+                                                  "num_key_value_heads": 4, "clip_qkv": None}),
+    "phi2": ("PhiConfig", "PhiForCausalLM", {"partial_rotary_factor": 0.5, "hidden_act": "gelu_new", "layer_norm_eps": 1e-5, "intermediate_size": 1024,
+                                             "qk_layernorm": False, "tie_word_embeddings": False}),
     "command-r": ("CohereConfig", "CohereForCausalLM", {"logit_scale": 0.0625, "layer_norm_eps": 1e-5, "use_qk_norm": False, "tie_word_embeddings": True}),
     "qwen3moe": ("Qwen3MoeConfig", "Qwen3MoeForCausalLM", {"head_dim": 64, "moe_intermediate_size": 128, "num_experts": 4,
                                                              "num_experts_per_tok": 2, "norm_topk_prob": True}),

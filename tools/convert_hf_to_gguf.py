@@ -27,11 +27,11 @@ ARCHS = {"LlamaForCausalLM": "llama", "MistralForCausalLM": "llama", "MixtralFor
          "SmolLM3ForCausalLM": "smollm3", "SeedOssForCausalLM": "seed_oss", "Ernie4_5ForCausalLM": "ernie4_5", "GraniteMoeForCausalLM": "granitemoe",
          "Starcoder2ForCausalLM": "starcoder2", "FalconForCausalLM": "falcon", "OlmoForCausalLM": "olmo", "CohereForCausalLM": "command-r",
          "GPTNeoXForCausalLM": "gptneox", "StableLmForCausalLM": "stablelm", "NemotronForCausalLM": "nemotron", "ArceeForCausalLM": "arcee",
-         "GPT2LMHeadModel": "gpt2", "GPTBigCodeForCausalLM": "starcoder", "Olmo2ForCausalLM": "olmo2", "Glm4ForCausalLM": "glm4"}
+         "GPT2LMHeadModel": "gpt2", "GPTBigCodeForCausalLM": "starcoder", "Olmo2ForCausalLM": "olmo2", "Glm4ForCausalLM": "glm4", "PhiForCausalLM": "phi2", "OlmoeForCausalLM": "olmoe"}
 # families whose GGUF graph rotates adjacent pairs: HF's half-split Q/K rows are permuted on the way in (ernie4_5 already stores
 # adjacent pairs upstream, so it is not in the list)
 PERMUTE_QK = ("llama", "granite", "granitemoe", "smollm3", "olmo", "arcee")
-LAYERNORM = ("starcoder2", "falcon", "olmo", "command-r", "gptneox", "stablelm", "nemotron", "gpt2", "starcoder")
+LAYERNORM = ("starcoder2", "falcon", "olmo", "command-r", "gptneox", "stablelm", "nemotron", "gpt2", "starcoder", "phi2")
 LAYER_MAP = {
     "input_layernorm.weight": "attn_norm.weight", "post_attention_layernorm.weight": "ffn_norm.weight",
     "self_attn.q_proj.weight": "attn_q.weight", "self_attn.k_proj.weight": "attn_k.weight", "self_attn.v_proj.weight": "attn_v.weight",
@@ -46,6 +46,9 @@ LAYER_MAP = {
     # LayerNorm families: norm and projection biases, starcoder2's non-gated MLP
     "input_layernorm.bias": "attn_norm.bias", "post_attention_layernorm.bias": "ffn_norm.bias", "self_attn.o_proj.bias": "attn_output.bias",
     "mlp.c_fc.weight": "ffn_up.weight", "mlp.c_fc.bias": "ffn_up.bias", "mlp.c_proj.weight": "ffn_down.weight", "mlp.c_proj.bias": "ffn_down.bias",
+    # phi (phi-1 / phi-1.5 / phi-2)
+    "self_attn.dense.weight": "attn_output.weight", "self_attn.dense.bias": "attn_output.bias",
+    "mlp.fc1.weight": "ffn_up.weight", "mlp.fc1.bias": "ffn_up.bias", "mlp.fc2.weight": "ffn_down.weight", "mlp.fc2.bias": "ffn_down.bias",
 }
 # falcon keeps its own module names (transformer.h.N....); QKV is regrouped separately
 FALCON_MAP = {"input_layernorm.weight": "attn_norm.weight", "input_layernorm.bias": "attn_norm.bias",
@@ -65,7 +68,8 @@ TOP_MAP = {"model.embed_tokens.weight": "token_embd.weight", "model.norm.weight"
            "transformer.ln_f.weight": "output_norm.weight", "transformer.ln_f.bias": "output_norm.bias",
            "transformer.wte.weight": "token_embd.weight", "transformer.wpe.weight": "position_embd.weight",
            "gpt_neox.embed_in.weight": "token_embd.weight", "gpt_neox.final_layer_norm.weight": "output_norm.weight",
-           "gpt_neox.final_layer_norm.bias": "output_norm.bias", "embed_out.weight": "output.weight"}
+           "gpt_neox.final_layer_norm.bias": "output_norm.bias", "embed_out.weight": "output.weight",
+           "model.final_layernorm.weight": "output_norm.weight", "model.final_layernorm.bias": "output_norm.bias", "lm_head.bias": "output.bias"}
 
 
 def permute_qk(w: np.ndarray, n_head: int) -> np.ndarray:
@@ -197,7 +201,7 @@ def convert(src: str, dst: str, outtype: str = "F16") -> str:
     else:
         w.add(f"{a}.attention.layer_norm_rms_epsilon", float(cfg.get("rms_norm_eps", 1e-5)), ValueType.FLOAT32)
     w.add(f"{a}.rope.freq_base", theta, ValueType.FLOAT32)
-    rot = (cfg.get("rotary_pct") or cfg.get("partial_rotary_factor") or rope.get("partial_rotary_factor")) if a in ("gptneox", "stablelm", "nemotron", "glm4") else None
+    rot = (cfg.get("rotary_pct") or cfg.get("partial_rotary_factor") or rope.get("partial_rotary_factor")) if a in ("gptneox", "stablelm", "nemotron", "glm4", "phi2") else None
     w.add(f"{a}.rope.dimension_count", int(D * float(rot)) if rot else D, ValueType.UINT32)
     if a == "gptneox":
         w.add(f"{a}.use_parallel_residual", bool(cfg.get("use_parallel_residual", True)))
