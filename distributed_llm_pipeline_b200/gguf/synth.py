@@ -173,12 +173,13 @@ def _tensor_plan(cfg: ModelConfig, rope_freqs: bool):
                 plan += [(p + "ffn_up.bias", (F,), il, 0.05), (p + "ffn_down.bias", (E,), il, 0.05)]
         elif cfg.fused_gate_up:
             plan += [(p + "ffn_up.weight", (2 * F, E), il, 0.02), (p + "ffn_down.weight", (E, F), il, 0.02)]
-        elif cfg.is_moe and il < cfg.n_layer_dense_lead:      # deepseek / bailingmoe: dense lead layers with their own width
+        elif cfg.is_moe and not cfg.layer_is_moe(il):      # deepseek / bailingmoe / glm4moe: dense lead layers with their own width (ernie4_5-moe: interleaved too)
             Fd = cfg.n_ff_dense or F
             plan += [(p + "ffn_gate.weight", (Fd, E), il, 0.02), (p + "ffn_down.weight", (E, Fd), il, 0.02), (p + "ffn_up.weight", (Fd, E), il, 0.02)]
         elif cfg.is_moe:
             plan += [
                 (p + "ffn_gate_inp.weight", (cfg.n_expert, E), il, 0.02),
+                *([(p + "exp_probs_b.bias", (cfg.n_expert,), il, 0.05)] if cfg.moe_sel_bias else []),
                 (p + "ffn_gate_exps.weight", (cfg.n_expert, F, E), il, 0.02),
                 (p + "ffn_down_exps.weight", (cfg.n_expert, E, F), il, 0.02),
                 (p + "ffn_up_exps.weight", (cfg.n_expert, F, E), il, 0.02),
@@ -257,14 +258,19 @@ def write_synthetic_gguf(path: str, cfg: ModelConfig, ftype: str = "F16", seed: 
             w.add(f"{a}.expert_feed_forward_length", cfg.n_ff, ValueType.UINT32)
         w.add(f"{a}.expert_count", cfg.n_expert, ValueType.UINT32)
         w.add(f"{a}.expert_used_count", cfg.n_expert_used, ValueType.UINT32)
-        if cfg.n_ff_shared and a not in ("deepseek", "bailingmoe"):
+        if cfg.n_ff_shared and a not in ("deepseek", "bailingmoe", "glm4moe", "dots1"):
             w.add(f"{a}.expert_shared_feed_forward_length", cfg.n_ff_shared, ValueType.UINT32)
-        if a in ("deepseek", "bailingmoe"):
+        if a == "ernie4_5-moe":
+            w.add(f"{a}.leading_dense_block_count", cfg.n_layer_dense_lead, ValueType.UINT32)
+            w.add(f"{a}.interleave_moe_layer_step", cfg.moe_layer_step, ValueType.UINT32)
+        if a in ("deepseek", "bailingmoe", "glm4moe", "dots1"):
             w.add(f"{a}.leading_dense_block_count", cfg.n_layer_dense_lead, ValueType.UINT32)
             w.add(f"{a}.expert_shared_count", cfg.n_ff_shared // cfg.n_ff, ValueType.UINT32)
             w.add(f"{a}.expert_weights_scale", float(cfg.expert_weights_scale), ValueType.FLOAT32)
-            if a == "bailingmoe":
+            if a in ("bailingmoe", "glm4moe", "dots1"):
                 w.add(f"{a}.expert_weights_norm", bool(cfg.moe_norm_topk))
+            if a in ("glm4moe", "dots1"):
+                w.add(f"{a}.expert_gating_func", 2 if cfg.moe_gating == "sigmoid" else 1, ValueType.UINT32)
     if vocab:
         toks, scores, types = synthetic_vocab(cfg.vocab_size)
         w.add("tokenizer.ggml.model", "llama")

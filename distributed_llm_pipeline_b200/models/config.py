@@ -54,8 +54,14 @@ class ModelConfig:
     # deepseek (v1), bailingmoe: the first layers are dense (their own FFN width), routed weights are multiplied by a constant, and the
     # shared experts are added without a gate (`llama.cpp/src/models/deepseek.cpp:86-120`)
     n_layer_dense_lead: int = 0
+    moe_layer_step: int = 1        # ernie4_5-moe: behind the lead layers only every step-th layer routes, the others are dense
     n_ff_dense: int = 0            # FFN width of the dense lead layers (0: n_ff)
-    expert_weights_scale: float = 1.0      # read and written back, not applied: the reference's builders for these two families pass scale_w = false
+    expert_weights_scale: float = 1.0      # read and written back; applied only with moe_scale_w (the deepseek-v1 / bailingmoe builders pass scale_w = false)
+    # glm4moe (GLM-4.5), dots1: DeepSeek-V3 style routing - sigmoid scores, a per-expert bias added for the SELECTION only, weights = the
+    # unbiased scores of the selected experts (renormalised when the file says so) times expert_weights_scale (llama-graph.cpp:1037-1143)
+    moe_gating: str = "softmax"    # "softmax" | "sigmoid"
+    moe_sel_bias: bool = False     # `blk.N.exp_probs_b.bias`
+    moe_scale_w: bool = False
     # LayerNorm / GELU / parallel-residual families (starcoder2, falcon, olmo, orion, command-r): the generic layer path
     norm_type: str = "rms"         # "rms" | "layer" (mean-centred; weight and bias optional per file: olmo has neither)
     ffn_act: str = "swiglu"        # "swiglu" (gated SiLU) | "gelu" | "relu2" (non-gated: ffn_up -> activation -> ffn_down, biases optional)
@@ -81,7 +87,10 @@ class ModelConfig:
     @property
     def ffn_norm_name(self) -> str:
         """Tensor holding the pre-FFN norm weight: seed_oss files call it post_attention_norm (`llama.cpp/src/models/seed-oss.cpp:86`)."""
-        return "post_attention_norm.weight" if self.arch == "seed_oss" else "ffn_norm.weight"
+        return "post_attention_norm.weight" if self.arch in ("seed_oss", "glm4moe") else "ffn_norm.weight"
+
+    def layer_is_moe(self, il: int) -> bool:
+        return self.n_expert > 0 and il >= self.n_layer_dense_lead and (il + 1) % max(1, self.moe_layer_step) == 0
 
     def layer_uses_rope(self, il: int) -> bool:
         return self.no_rope_step <= 0 or (il + 1) % self.no_rope_step != 0
@@ -234,6 +243,17 @@ PRESETS: dict[str, ModelConfig] = {
     "tiny-olmoe": ModelConfig(name="tiny-olmoe", arch="olmoe", vocab_size=512, n_embd=256, n_layer=2, n_head=4, n_head_kv=4, head_dim=64, n_ff=256,
                               n_ctx_train=512, rope_theta=10000.0, rope_dim=64, rope_neox=True, qk_norm_full=True, n_expert=4, n_expert_used=2,
                               moe_norm_topk=False),
+    "tiny-glm4moe": ModelConfig(name="tiny-glm4moe", arch="glm4moe", vocab_size=512, n_embd=256, n_layer=3, n_head=4, n_head_kv=2, head_dim=64, n_ff=256,
+                                n_ctx_train=512, rope_theta=10000.0, rope_dim=32, rope_neox=True, qkv_bias=True, qk_norm=True, n_expert=4, n_expert_used=2,
+                                moe_norm_topk=True, n_ff_shared=256, n_layer_dense_lead=1, n_ff_dense=512, expert_weights_scale=1.5,
+                                moe_gating="sigmoid", moe_sel_bias=True, moe_scale_w=True),
+    "tiny-dots1": ModelConfig(name="tiny-dots1", arch="dots1", vocab_size=512, n_embd=256, n_layer=3, n_head=4, n_head_kv=4, head_dim=64, n_ff=256,
+                              n_ctx_train=512, rope_theta=10000.0, rope_dim=64, rope_neox=True, qk_norm=True, n_expert=4, n_expert_used=2,
+                              moe_norm_topk=True, n_ff_shared=256, n_layer_dense_lead=1, n_ff_dense=512, expert_weights_scale=2.5,
+                              moe_gating="sigmoid", moe_sel_bias=True, moe_scale_w=True),
+    "tiny-ernie-moe": ModelConfig(name="tiny-ernie-moe", arch="ernie4_5-moe", vocab_size=512, n_embd=256, n_layer=4, n_head=4, n_head_kv=2, head_dim=64, n_ff=256,
+                                  n_ctx_train=512, rope_theta=10000.0, rope_dim=64, n_expert=4, n_expert_used=2, moe_norm_topk=True, n_ff_shared=256,
+                                  n_layer_dense_lead=1, n_ff_dense=512, moe_sel_bias=True),
     "tiny-exaone4": ModelConfig(name="tiny-exaone4", arch="exaone4", vocab_size=512, n_embd=256, n_layer=2, n_head=4, n_head_kv=2, head_dim=64, n_ff=512,
                                 n_ctx_train=512, rope_theta=10000.0, rope_dim=64, rope_neox=True, qk_norm=True, post_norm=True, pre_norm=False),
     "tiny-command-r": ModelConfig(name="tiny-command-r", arch="command-r", vocab_size=512, n_embd=256, n_layer=2, n_head=4, n_head_kv=2,
@@ -275,8 +295,8 @@ PRESETS: dict[str, ModelConfig] = {
 SUPPORTED_ARCHS = {"llama", "qwen2", "qwen2moe", "qwen3", "qwen3moe", "phi3", "granite",
                    "internlm2", "xverse", "ernie4_5", "exaone", "seed_oss", "minicpm", "granitemoe", "smollm3",
                    "starcoder2", "falcon", "olmo", "orion", "command-r", "gptneox", "stablelm", "nemotron", "arcee",
-                   "gpt2", "starcoder", "codeshell", "qwen", "baichuan", "olmo2", "glm4", "mistral3", "pangu-embedded", "chatglm", "plamo", "deepseek", "bailingmoe", "qwen2vl", "qwen3vl", "exaone4", "phi2", "olmoe", "qwen3vlmoe"}
-ROPE_NORM_ARCHS = {"llama", "granite", "granitemoe", "minicpm", "internlm2", "xverse", "ernie4_5", "smollm3", "olmo", "command-r", "arcee", "baichuan", "glm4", "mistral3", "chatglm", "deepseek", "bailingmoe"}     # llama_model_rope_type
+                   "gpt2", "starcoder", "codeshell", "qwen", "baichuan", "olmo2", "glm4", "mistral3", "pangu-embedded", "chatglm", "plamo", "deepseek", "bailingmoe", "qwen2vl", "qwen3vl", "exaone4", "phi2", "olmoe", "qwen3vlmoe", "glm4moe", "dots1", "ernie4_5-moe"}
+ROPE_NORM_ARCHS = {"llama", "granite", "granitemoe", "minicpm", "internlm2", "xverse", "ernie4_5", "ernie4_5-moe", "smollm3", "olmo", "command-r", "arcee", "baichuan", "glm4", "mistral3", "chatglm", "deepseek", "bailingmoe"}     # llama_model_rope_type
 # LayerNorm families and what differs beyond the norm (llama.cpp/src/models/{starcoder2,falcon,olmo,orion,command-r}.cpp):
 #   starcoder2: biases on every matrix, non-gated GELU MLP;  falcon: fused QKV, GELU MLP, attention and MLP in parallel from the same
 #   (or a second) norm;  olmo: norms without parameters;  orion: llama with LayerNorm;  command-r: parallel, logits * logit_scale
@@ -328,7 +348,7 @@ def config_from_gguf(meta: dict[str, Any], tensors: dict | None = None) -> Model
                     yarn_ext_factor=float(g("rope.scaling.yarn_ext_factor", 1.0)), yarn_attn_factor=float(g("rope.scaling.attn_factor", 1.0)),
                     yarn_beta_fast=float(g("rope.scaling.yarn_beta_fast", 32.0)), yarn_beta_slow=float(g("rope.scaling.yarn_beta_slow", 1.0)))
     tie = tensors is not None and "output.weight" not in tensors
-    n_layer = int(g("block_count"))
+    n_layer = int(g("block_count")) - int(g("nextn_predict_layers", 0) or 0)      # trailing multi-token-prediction layers are not part of the forward pass (glm4-moe.cpp:24)
     if arch == "exaone4" and (n_layer == 64 or int(g("attention.sliding_window", 0) or 0) > 0):
         raise NotImplementedError("exaone4 checkpoints with sliding-window layers (the 32B model) are not supported")
     if arch == "mistral3" and float(g("attention.temperature_scale", 0.0) or 0.0) != 0.0:
@@ -341,7 +361,7 @@ def config_from_gguf(meta: dict[str, Any], tensors: dict | None = None) -> Model
         dict(embedding_scale=1.0, residual_scale=1.0, logit_scale=1.0)
     return ModelConfig(
         name=str(meta.get("general.name", arch)), arch=arch, vocab_size=int(vocab), n_embd=n_embd,
-        n_layer=int(g("block_count")), n_head=n_head, n_head_kv=n_head_kv, head_dim=head_dim,
+        n_layer=n_layer, n_head=n_head, n_head_kv=n_head_kv, head_dim=head_dim,
         n_ff=int(g("expert_feed_forward_length") or g("feed_forward_length")) if int(g("expert_count", 0) or 0) > 0
         else int(g("feed_forward_length")) // (2 if arch == "qwen" else 1),      # qwen v1 files store twice the MLP width (llama-model.cpp: n_ff/2)
         n_ctx_train=int(g("context_length", 2048)),
@@ -355,10 +375,13 @@ def config_from_gguf(meta: dict[str, Any], tensors: dict | None = None) -> Model
         embedding_scale=float(g("embedding_scale") or dflt["embedding_scale"]), residual_scale=float(g("residual_scale") or dflt["residual_scale"]),
         logit_scale=(1.0 / float(g("logit_scale") or 1.0)) if arch == "command-r" else float(g("logit_scale") or dflt["logit_scale"]), attention_scale=float(g("attention.scale", 0.0) or 0.0),
         no_rope_step=4 if arch == "smollm3" else 1 if arch in LEARNED_POS_ARCHS else 0, learned_pos=arch in LEARNED_POS_ARCHS,
-        moe_norm_topk=bool(g("expert_weights_norm", False)) if arch == "bailingmoe" else arch not in ("qwen2moe", "deepseek", "olmoe"),
+        moe_gating="sigmoid" if ((arch == "glm4moe" and int(g("expert_gating_func", 0) or 0) in (0, 2)) or (arch == "dots1" and int(g("expert_gating_func", 0) or 0) == 2)) else "softmax",
+        moe_sel_bias=tensors is not None and any(k.endswith(".exp_probs_b.bias") for k in tensors), moe_scale_w=arch in ("glm4moe", "dots1"),
+        moe_layer_step=int(g("interleave_moe_layer_step", 1) or 1),
+        moe_norm_topk=bool(g("expert_weights_norm", False)) if arch in ("bailingmoe", "glm4moe", "dots1") else arch not in ("qwen2moe", "deepseek", "olmoe"),
         n_ff_shared=int(g("expert_shared_feed_forward_length", 0) or 0) or (int(g("expert_shared_count", 0) or 0) * int(g("expert_feed_forward_length", 0) or 0)),
         n_layer_dense_lead=int(g("leading_dense_block_count", 0) or 0), expert_weights_scale=float(g("expert_weights_scale", 1.0) or 1.0),
-        n_ff_dense=int(g("feed_forward_length")) if int(g("leading_dense_block_count", 0) or 0) > 0 else 0,
+        n_ff_dense=int(g("feed_forward_length")) if (int(g("leading_dense_block_count", 0) or 0) > 0 or int(g("interleave_moe_layer_step", 1) or 1) > 1) else 0,
         qkv_bias=arch in ("qwen2", "qwen2moe", "qwen2vl") or (tensors is not None and ("blk.0.attn_q.bias" in tensors or "blk.0.attn_qkv.bias" in tensors)),
         qk_norm=arch in ("qwen3", "qwen3moe", "qwen3vl", "qwen3vlmoe") or (arch not in ("olmo2", "olmoe") and tensors is not None and "blk.0.attn_q_norm.weight" in tensors),
         fused_qkv=arch == "phi3" or (tensors is not None and "blk.0.attn_qkv.weight" in tensors),

@@ -187,10 +187,16 @@ class ReferenceModel:
             u = self.mm(x, p + "ffn_up.weight")
             return self.mm(torch.nn.functional.silu(g) * u, p + "ffn_down.weight")
         logits = self.mm(x, p + "ffn_gate_inp.weight")
-        probs = torch.softmax(logits, dim=-1)
-        topw, topi = probs.topk(c.n_expert_used, dim=-1)
+        probs = torch.sigmoid(logits) if c.moe_gating == "sigmoid" else torch.softmax(logits, dim=-1)
+        if p + "exp_probs_b.bias" in w:      # the bias steers which experts are picked; their weights are the unbiased scores
+            topi = (probs + w[p + "exp_probs_b.bias"]).topk(c.n_expert_used, dim=-1).indices
+            topw = probs.gather(-1, topi)
+        else:
+            topw, topi = probs.topk(c.n_expert_used, dim=-1)
         if c.moe_norm_topk:
-            topw = topw / topw.sum(-1, keepdim=True)
+            topw = topw / topw.sum(-1, keepdim=True).clamp_min(6.103515625e-5)
+        if c.moe_scale_w:
+            topw = topw * c.expert_weights_scale
         out = torch.zeros_like(x)
         if c.n_ff_shared:   # qwen2moe: shared expert, scaled by sigmoid(x . gate_vector)  (llama.cpp/src/models/qwen2moe.cpp)
             g = self.mm(x, p + "ffn_gate_shexp.weight")

@@ -36,6 +36,7 @@ class LayerWeights:
     # MoE
     router: torch.Tensor | None = None                 # fp32 [n_expert, E]
     shared_gate: torch.Tensor | None = None            # fp32 [E]: sigmoid gate of the shared expert (qwen2moe; w_gate/w_up/w_down hold it)
+    sel_bias: torch.Tensor | None = None               # fp32 [n_expert]: added to the router scores for the expert selection only (glm4moe)
     e_gate: list[DeviceWeight] = field(default_factory=list)
     e_up: list[DeviceWeight] = field(default_factory=list)
     e_down: list[DeviceWeight] = field(default_factory=list)
@@ -269,6 +270,9 @@ def load_weights(src: str | GGUFModelFiles, device, layer_range: range | None = 
             lw.qkv_bias = torch.cat([bq, bk, bv]).contiguous()
         if cfg.qk_norm:
             lw.q_norm, lw.k_norm = f32(p + "attn_q_norm.weight"), f32(p + "attn_k_norm.weight")
+            if perm_q is not None:      # partial rotary (glm4moe): the per-head norm weights follow the re-ordered rows of their head
+                one = torch.as_tensor(perm_q[:D], device=lw.q_norm.device)
+                lw.q_norm, lw.k_norm = lw.q_norm[one].contiguous(), lw.k_norm[one].contiguous()
         f0, f1 = _split(cfg.n_ff, tp_size, tp_rank, 256 if tp_size > 1 else 1)
         if cfg.ffn_act in ("gelu", "relu2"):     # non-gated MLP: up -> activation -> down
             lw.w_up = mat(p + "ffn_up.weight", rows=(f0, f1))
@@ -281,10 +285,12 @@ def load_weights(src: str | GGUFModelFiles, device, layer_range: range | None = 
             lw.w_down = mat(p + "ffn_down.weight", cols=(f0, f1), scale=cfg.residual_scale)
         elif cfg.is_moe and p + "ffn_gate_inp.weight" in f:
             lw.router = f32(p + "ffn_gate_inp.weight")
+            lw.sel_bias = f32(p + "exp_probs_b.bias") if p + "exp_probs_b.bias" in f else None
+            w_scale = cfg.expert_weights_scale if cfg.moe_scale_w else 1.0     # a constant on the routed weights: folded into the down projections
             for e in range(cfg.n_expert):
                 lw.e_gate.append(mat(p + "ffn_gate_exps.weight", rows=(f0, f1), sub=e))
                 lw.e_up.append(mat(p + "ffn_up_exps.weight", rows=(f0, f1), sub=e))
-                lw.e_down.append(mat(p + "ffn_down_exps.weight", cols=(f0, f1), sub=e, scale=cfg.residual_scale))
+                lw.e_down.append(mat(p + "ffn_down_exps.weight", cols=(f0, f1), sub=e, scale=cfg.residual_scale * w_scale))
             if dev.type == "cuda" and all(w.wtype == lw.e_gate[0].wtype for w in lw.e_gate + lw.e_up) and \
                     all(w.wtype == lw.e_down[0].wtype for w in lw.e_down):
                 def restack(ws):

@@ -63,6 +63,15 @@ CASES = {
     "olmo": ("OlmoConfig", "OlmoForCausalLM", {"clip_qkv": None, "num_key_value_heads": 4}),
     "olmoe": ("OlmoeConfig", "OlmoeForCausalLM", {"intermediate_size": 128, "num_experts": 4, "num_experts_per_tok": 2, "norm_topk_prob": False,
                                                   "num_key_value_heads": 4, "clip_qkv": None}),
+    "glm4moe": ("Glm4MoeConfig", "Glm4MoeForCausalLM", {"num_hidden_layers": 3, "head_dim": 64, "moe_intermediate_size": 128, "num_experts_per_tok": 2,
+                                                        "n_shared_experts": 1, "n_routed_experts": 4, "routed_scaling_factor": 1.5, "first_k_dense_replace": 1,
+                                                        "use_qk_norm": True, "attention_bias": True, "norm_topk_prob": True}),
+    "dots1": ("Dots1Config", "Dots1ForCausalLM", {"num_hidden_layers": 3, "num_key_value_heads": 4, "head_dim": 64, "moe_intermediate_size": 128,
+                                                  "num_experts_per_tok": 2, "n_shared_experts": 1, "n_routed_experts": 4, "routed_scaling_factor": 2.5,
+                                                  "first_k_dense_replace": 1, "norm_topk_prob": True, "sliding_window": None,
+                                                  "layer_types": ["full_attention"] * 3}),
+    "ernie4_5-moe": ("Ernie4_5_MoeConfig", "Ernie4_5_MoeForCausalLM", {"num_hidden_layers": 3, "moe_intermediate_size": 128, "moe_k": 2, "moe_num_experts": 4,
+                                                                        "moe_num_shared_experts": 1, "moe_layer_start_index": 1, "use_bias": False, "head_dim": 64}),
     "phi2": ("PhiConfig", "PhiForCausalLM", {"partial_rotary_factor": 0.5, "hidden_act": "gelu_new", "layer_norm_eps": 1e-5, "intermediate_size": 1024,
                                              "qk_layernorm": False, "tie_word_embeddings": False}),
     "command-r": ("CohereConfig", "CohereForCausalLM", {"logit_scale": 0.0625, "layer_norm_eps": 1e-5, "use_qk_norm": False, "tie_word_embeddings": True}),
@@ -96,7 +105,7 @@ def test_converted_model_matches_hf_forward(tmp_path, family):
     with torch.no_grad():
         want = model(torch.tensor([ids])).logits[0]
     ref = ReferenceModel.from_gguf(out)
-    assert ref.cfg.arch == ("llama" if family in ("llama", "llama31", "mistral", "mixtral") else "command-r" if family == "command-r" else family.split("-")[0])
+    assert ref.cfg.arch == ("llama" if family in ("llama", "llama31", "mistral", "mixtral") else family if family in ("command-r", "ernie4_5-moe") else family.split("-")[0])
     if family == "qwen2-yarn":
         assert ref.cfg.yarn_factor == 4.0 and ref.cfg.yarn_orig_ctx == 128
     if family == "llama31":

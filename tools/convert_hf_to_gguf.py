@@ -27,7 +27,8 @@ ARCHS = {"LlamaForCausalLM": "llama", "MistralForCausalLM": "llama", "MixtralFor
          "SmolLM3ForCausalLM": "smollm3", "SeedOssForCausalLM": "seed_oss", "Ernie4_5ForCausalLM": "ernie4_5", "GraniteMoeForCausalLM": "granitemoe",
          "Starcoder2ForCausalLM": "starcoder2", "FalconForCausalLM": "falcon", "OlmoForCausalLM": "olmo", "CohereForCausalLM": "command-r",
          "GPTNeoXForCausalLM": "gptneox", "StableLmForCausalLM": "stablelm", "NemotronForCausalLM": "nemotron", "ArceeForCausalLM": "arcee",
-         "GPT2LMHeadModel": "gpt2", "GPTBigCodeForCausalLM": "starcoder", "Olmo2ForCausalLM": "olmo2", "Glm4ForCausalLM": "glm4", "PhiForCausalLM": "phi2", "OlmoeForCausalLM": "olmoe"}
+         "GPT2LMHeadModel": "gpt2", "GPTBigCodeForCausalLM": "starcoder", "Olmo2ForCausalLM": "olmo2", "Glm4ForCausalLM": "glm4", "PhiForCausalLM": "phi2", "OlmoeForCausalLM": "olmoe", "Glm4MoeForCausalLM": "glm4moe", "Dots1ForCausalLM": "dots1",
+         "Ernie4_5_MoeForCausalLM": "ernie4_5-moe"}
 # families whose GGUF graph rotates adjacent pairs: HF's half-split Q/K rows are permuted on the way in (ernie4_5 already stores
 # adjacent pairs upstream, so it is not in the list)
 PERMUTE_QK = ("llama", "granite", "granitemoe", "smollm3", "olmo", "arcee")
@@ -182,12 +183,25 @@ def convert(src: str, dst: str, outtype: str = "F16") -> str:
         w.add(f"{a}.residual_scale", float(cfg.get("residual_multiplier", 1.0)), ValueType.FLOAT32)
         w.add(f"{a}.logit_scale", float(cfg.get("logits_scaling", 1.0)), ValueType.FLOAT32)
         w.add(f"{a}.attention.scale", float(cfg.get("attention_multiplier", 1.0)), ValueType.FLOAT32)
-    n_exp = int(cfg.get("num_local_experts") or cfg.get("num_experts") or 0)
+    n_exp = int(cfg.get("num_local_experts") or cfg.get("num_experts") or cfg.get("n_routed_experts") or cfg.get("moe_num_experts") or 0)
     if n_exp:
         w.add(f"{a}.expert_count", n_exp, ValueType.UINT32)
-        w.add(f"{a}.expert_used_count", int(cfg.get("num_experts_per_tok", 2)), ValueType.UINT32)
+        w.add(f"{a}.expert_used_count", int(cfg.get("num_experts_per_tok") or cfg.get("moe_k") or 2), ValueType.UINT32)
         if cfg.get("moe_intermediate_size"):
             w.add(f"{a}.expert_feed_forward_length", int(cfg["moe_intermediate_size"]), ValueType.UINT32)
+        if a == "ernie4_5-moe":
+            if cfg.get("moe_layer_interval", 1) != 1 or cfg.get("moe_layer_end_index", L - 1) not in (-1, L - 1):
+                raise SystemExit("ernie4_5-moe: only checkpoints whose layers all route behind the dense lead layers are supported (as in the reference loader)")
+            w.add(f"{a}.leading_dense_block_count", int(cfg.get("moe_layer_start_index", 0)), ValueType.UINT32)
+            w.add(f"{a}.interleave_moe_layer_step", 1, ValueType.UINT32)
+            if cfg.get("moe_num_shared_experts"):
+                w.add(f"{a}.expert_shared_feed_forward_length", int(cfg["moe_num_shared_experts"]) * int(cfg["moe_intermediate_size"]), ValueType.UINT32)
+        if a in ("glm4moe", "dots1"):      # DeepSeek-V3 style routing: sigmoid scores, selection bias, scaled weights, dense lead layers, ungated shared experts
+            w.add(f"{a}.expert_shared_count", int(cfg.get("n_shared_experts", 1)), ValueType.UINT32)
+            w.add(f"{a}.leading_dense_block_count", int(cfg.get("first_k_dense_replace", 0)), ValueType.UINT32)
+            w.add(f"{a}.expert_weights_scale", float(cfg.get("routed_scaling_factor", 1.0)), ValueType.FLOAT32)
+            w.add(f"{a}.expert_weights_norm", bool(cfg.get("norm_topk_prob", True)))
+            w.add(f"{a}.expert_gating_func", 2, ValueType.UINT32)
         if a == "qwen2moe" and cfg.get("shared_expert_intermediate_size"):
             w.add(f"{a}.expert_shared_feed_forward_length", int(cfg["shared_expert_intermediate_size"]), ValueType.UINT32)
     w.add(f"{a}.attention.head_count", H, ValueType.UINT32)
@@ -201,7 +215,7 @@ def convert(src: str, dst: str, outtype: str = "F16") -> str:
     else:
         w.add(f"{a}.attention.layer_norm_rms_epsilon", float(cfg.get("rms_norm_eps", 1e-5)), ValueType.FLOAT32)
     w.add(f"{a}.rope.freq_base", theta, ValueType.FLOAT32)
-    rot = (cfg.get("rotary_pct") or cfg.get("partial_rotary_factor") or rope.get("partial_rotary_factor")) if a in ("gptneox", "stablelm", "nemotron", "glm4", "phi2") else None
+    rot = (cfg.get("rotary_pct") or cfg.get("partial_rotary_factor") or rope.get("partial_rotary_factor")) if a in ("gptneox", "stablelm", "nemotron", "glm4", "phi2", "glm4moe") else None
     w.add(f"{a}.rope.dimension_count", int(D * float(rot)) if rot else D, ValueType.UINT32)
     if a == "gptneox":
         w.add(f"{a}.use_parallel_residual", bool(cfg.get("use_parallel_residual", True)))
@@ -248,7 +262,11 @@ def convert(src: str, dst: str, outtype: str = "F16") -> str:
             continue
         il, rest = m.group(1), m.group(2)
         t = tensors[name]
-        if rest.startswith("shared_expert"):
+        if rest.startswith("shared_experts."):       # glm4moe: always-on experts, no gate
+            tensors[f"__moe__.blk.{il}.ffn_{rest.split('.')[1].split('_')[0]}_shexp.weight"] = tensors.pop(name)
+        elif rest in ("gate.e_score_correction_bias", "gate.moe_statics.e_score_correction_bias", "moe_statics.e_score_correction_bias"):
+            tensors[f"__moe__.blk.{il}.exp_probs_b.bias"] = tensors.pop(name).reshape(-1)
+        elif rest.startswith("shared_expert"):
             sh = {"shared_expert_gate.weight": "ffn_gate_inp_shexp.weight", "shared_expert.gate_proj.weight": "ffn_gate_shexp.weight",
                   "shared_expert.up_proj.weight": "ffn_up_shexp.weight", "shared_expert.down_proj.weight": "ffn_down_shexp.weight"}[rest]
             t2 = tensors.pop(name)
@@ -324,7 +342,7 @@ def convert(src: str, dst: str, outtype: str = "F16") -> str:
             out = out.replace("ffn_norm.weight", "post_attention_norm.weight")
         if a == "nemotron" and out.endswith("_norm.weight"):
             t = t + 1.0          # LayerNorm1p: the checkpoint stores weight - 1
-        if a == "seed_oss" and out.endswith("ffn_norm.weight"):
+        if a in ("seed_oss", "glm4moe") and out.endswith("ffn_norm.weight"):
             out = out.replace("ffn_norm.weight", "post_attention_norm.weight")
         if a in PERMUTE_QK and out.endswith("attn_q.weight"):
             t = permute_qk(t, H)
