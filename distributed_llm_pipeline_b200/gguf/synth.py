@@ -269,8 +269,8 @@ def write_synthetic_gguf(path: str, cfg: ModelConfig, ftype: str = "F16", seed: 
             w.add(f"{a}.expert_weights_scale", float(cfg.expert_weights_scale), ValueType.FLOAT32)
             if a in ("bailingmoe", "glm4moe", "dots1"):
                 w.add(f"{a}.expert_weights_norm", bool(cfg.moe_norm_topk))
-            if a in ("glm4moe", "dots1"):
-                w.add(f"{a}.expert_gating_func", 2 if cfg.moe_gating == "sigmoid" else 1, ValueType.UINT32)
+        if a in ("glm4moe", "dots1", "minimax-m2"):
+            w.add(f"{a}.expert_gating_func", 2 if cfg.moe_gating == "sigmoid" else 1, ValueType.UINT32)
     if vocab:
         toks, scores, types = synthetic_vocab(cfg.vocab_size)
         w.add("tokenizer.ggml.model", "llama")

@@ -254,6 +254,9 @@ PRESETS: dict[str, ModelConfig] = {
     "tiny-ernie-moe": ModelConfig(name="tiny-ernie-moe", arch="ernie4_5-moe", vocab_size=512, n_embd=256, n_layer=4, n_head=4, n_head_kv=2, head_dim=64, n_ff=256,
                                   n_ctx_train=512, rope_theta=10000.0, rope_dim=64, n_expert=4, n_expert_used=2, moe_norm_topk=True, n_ff_shared=256,
                                   n_layer_dense_lead=1, n_ff_dense=512, moe_sel_bias=True),
+    "tiny-minimax-m2": ModelConfig(name="tiny-minimax-m2", arch="minimax-m2", vocab_size=512, n_embd=256, n_layer=2, n_head=4, n_head_kv=2, head_dim=64, n_ff=256,
+                                   n_ctx_train=512, rope_theta=10000.0, rope_dim=32, rope_neox=True, qk_norm_full=True, n_expert=4, n_expert_used=2,
+                                   moe_norm_topk=True, moe_gating="sigmoid", moe_sel_bias=True),
     "tiny-exaone4": ModelConfig(name="tiny-exaone4", arch="exaone4", vocab_size=512, n_embd=256, n_layer=2, n_head=4, n_head_kv=2, head_dim=64, n_ff=512,
                                 n_ctx_train=512, rope_theta=10000.0, rope_dim=64, rope_neox=True, qk_norm=True, post_norm=True, pre_norm=False),
     "tiny-command-r": ModelConfig(name="tiny-command-r", arch="command-r", vocab_size=512, n_embd=256, n_layer=2, n_head=4, n_head_kv=2,
@@ -295,7 +298,7 @@ PRESETS: dict[str, ModelConfig] = {
 SUPPORTED_ARCHS = {"llama", "qwen2", "qwen2moe", "qwen3", "qwen3moe", "phi3", "granite",
                    "internlm2", "xverse", "ernie4_5", "exaone", "seed_oss", "minicpm", "granitemoe", "smollm3",
                    "starcoder2", "falcon", "olmo", "orion", "command-r", "gptneox", "stablelm", "nemotron", "arcee",
-                   "gpt2", "starcoder", "codeshell", "qwen", "baichuan", "olmo2", "glm4", "mistral3", "pangu-embedded", "chatglm", "plamo", "deepseek", "bailingmoe", "qwen2vl", "qwen3vl", "exaone4", "phi2", "olmoe", "qwen3vlmoe", "glm4moe", "dots1", "ernie4_5-moe"}
+                   "gpt2", "starcoder", "codeshell", "qwen", "baichuan", "olmo2", "glm4", "mistral3", "pangu-embedded", "chatglm", "plamo", "deepseek", "bailingmoe", "qwen2vl", "qwen3vl", "exaone4", "phi2", "olmoe", "qwen3vlmoe", "glm4moe", "dots1", "ernie4_5-moe", "minimax-m2"}
 ROPE_NORM_ARCHS = {"llama", "granite", "granitemoe", "minicpm", "internlm2", "xverse", "ernie4_5", "ernie4_5-moe", "smollm3", "olmo", "command-r", "arcee", "baichuan", "glm4", "mistral3", "chatglm", "deepseek", "bailingmoe"}     # llama_model_rope_type
 # LayerNorm families and what differs beyond the norm (llama.cpp/src/models/{starcoder2,falcon,olmo,orion,command-r}.cpp):
 #   starcoder2: biases on every matrix, non-gated GELU MLP;  falcon: fused QKV, GELU MLP, attention and MLP in parallel from the same
@@ -368,14 +371,14 @@ def config_from_gguf(meta: dict[str, Any], tensors: dict | None = None) -> Model
         rms_eps=float(g("attention.layer_norm_epsilon", 1e-5) if arch in LAYERNORM_ARCHS else g("attention.layer_norm_rms_epsilon", 1e-5)),
         norm_type="layer" if arch in LAYERNORM_ARCHS else "rms", ffn_act="gelu" if arch in ("starcoder2", "falcon", "gptneox", "gpt2", "starcoder", "codeshell", "phi2") else "relu2" if arch in ("nemotron", "arcee") else "swiglu",
         attn_out_bias=tensors is not None and "blk.0.attn_output.bias" in tensors and arch not in LAYERNORM_ARCHS,
-        post_norm=arch in ("olmo2", "glm4", "exaone4"), pre_norm=arch not in ("olmo2", "exaone4"), qk_norm_full=arch in ("olmo2", "olmoe"),
+        post_norm=arch in ("olmo2", "glm4", "exaone4"), pre_norm=arch not in ("olmo2", "exaone4"), qk_norm_full=arch in ("olmo2", "olmoe", "minimax-m2"),
         parallel_residual=arch in ("falcon", "command-r", "plamo", "phi2") or (arch == "gptneox" and bool(g("use_parallel_residual", True)))
         or (arch == "stablelm" and tensors is not None and "blk.0.ffn_norm.weight" not in tensors), fused_gate_up=arch in ("phi3", "glm4", "chatglm"), rope_theta=float(g("rope.freq_base", 10000.0)),
         rope_dim=int(g("rope.dimension_count", head_dim)), rope_neox=arch not in ROPE_NORM_ARCHS, rope_scale_linear=scale,
         embedding_scale=float(g("embedding_scale") or dflt["embedding_scale"]), residual_scale=float(g("residual_scale") or dflt["residual_scale"]),
         logit_scale=(1.0 / float(g("logit_scale") or 1.0)) if arch == "command-r" else float(g("logit_scale") or dflt["logit_scale"]), attention_scale=float(g("attention.scale", 0.0) or 0.0),
         no_rope_step=4 if arch == "smollm3" else 1 if arch in LEARNED_POS_ARCHS else 0, learned_pos=arch in LEARNED_POS_ARCHS,
-        moe_gating="sigmoid" if ((arch == "glm4moe" and int(g("expert_gating_func", 0) or 0) in (0, 2)) or (arch == "dots1" and int(g("expert_gating_func", 0) or 0) == 2)) else "softmax",
+        moe_gating="sigmoid" if ((arch == "glm4moe" and int(g("expert_gating_func", 0) or 0) in (0, 2)) or (arch in ("dots1", "minimax-m2") and int(g("expert_gating_func", 0) or 0) == 2)) else "softmax",
         moe_sel_bias=tensors is not None and any(k.endswith(".exp_probs_b.bias") for k in tensors), moe_scale_w=arch in ("glm4moe", "dots1"),
         moe_layer_step=int(g("interleave_moe_layer_step", 1) or 1),
         moe_norm_topk=bool(g("expert_weights_norm", False)) if arch in ("bailingmoe", "glm4moe", "dots1") else arch not in ("qwen2moe", "deepseek", "olmoe"),
@@ -383,7 +386,7 @@ def config_from_gguf(meta: dict[str, Any], tensors: dict | None = None) -> Model
         n_layer_dense_lead=int(g("leading_dense_block_count", 0) or 0), expert_weights_scale=float(g("expert_weights_scale", 1.0) or 1.0),
         n_ff_dense=int(g("feed_forward_length")) if (int(g("leading_dense_block_count", 0) or 0) > 0 or int(g("interleave_moe_layer_step", 1) or 1) > 1) else 0,
         qkv_bias=arch in ("qwen2", "qwen2moe", "qwen2vl") or (tensors is not None and ("blk.0.attn_q.bias" in tensors or "blk.0.attn_qkv.bias" in tensors)),
-        qk_norm=arch in ("qwen3", "qwen3moe", "qwen3vl", "qwen3vlmoe") or (arch not in ("olmo2", "olmoe") and tensors is not None and "blk.0.attn_q_norm.weight" in tensors),
+        qk_norm=arch in ("qwen3", "qwen3moe", "qwen3vl", "qwen3vlmoe") or (arch not in ("olmo2", "olmoe", "minimax-m2") and tensors is not None and "blk.0.attn_q_norm.weight" in tensors),
         fused_qkv=arch == "phi3" or (tensors is not None and "blk.0.attn_qkv.weight" in tensors),
         n_expert=int(g("expert_count", 0) or 0), n_expert_used=int(g("expert_used_count", 0) or 0),
         bos_id=int(meta.get("tokenizer.ggml.bos_token_id", 1)), eos_id=int(meta.get("tokenizer.ggml.eos_token_id", 2)),

@@ -259,6 +259,9 @@ def load_weights(src: str | GGUFModelFiles, device, layer_range: range | None = 
                 if tp_size > 1:
                     raise NotImplementedError("Q/K norms over the full projected width (olmo2) are not split across tensor-parallel ranks")
                 lw.q_norm_full, lw.k_norm_full = f32(p + "attn_q_norm.weight"), f32(p + "attn_k_norm.weight")
+                if perm_q is not None:      # partial rotary (minimax-m2): the norm weights follow the re-ordered projection rows
+                    lw.q_norm_full = lw.q_norm_full[torch.as_tensor(perm_q, device=dev)].contiguous()
+                    lw.k_norm_full = lw.k_norm_full[torch.as_tensor(perm_k, device=dev)].contiguous()
         if cfg.qkv_bias:
             if cfg.fused_qkv:       # gptneox: one bias vector laid out like the fused matrix
                 fb = f32(p + "attn_qkv.bias")

@@ -72,6 +72,10 @@ CASES = {
                                                   "layer_types": ["full_attention"] * 3}),
     "ernie4_5-moe": ("Ernie4_5_MoeConfig", "Ernie4_5_MoeForCausalLM", {"num_hidden_layers": 3, "moe_intermediate_size": 128, "moe_k": 2, "moe_num_experts": 4,
                                                                         "moe_num_shared_experts": 1, "moe_layer_start_index": 1, "use_bias": False, "head_dim": 64}),
+    "minimax-m2": ("MiniMaxM2Config", "MiniMaxM2ForCausalLM", {"intermediate_size": 128, "head_dim": 64, "num_local_experts": 4, "num_experts_per_tok": 2,
+                                                               "rope_parameters": {"rope_type": "default", "rope_theta": 10000.0, "partial_rotary_factor": 0.5}}),
+    "exaone4": ("Exaone4Config", "Exaone4ForCausalLM", {"head_dim": 64, "sliding_window": None, "sliding_window_pattern": None,
+                                                        "layer_types": ["full_attention", "full_attention"]}),
     "phi2": ("PhiConfig", "PhiForCausalLM", {"partial_rotary_factor": 0.5, "hidden_act": "gelu_new", "layer_norm_eps": 1e-5, "intermediate_size": 1024,
                                              "qk_layernorm": False, "tie_word_embeddings": False}),
     "command-r": ("CohereConfig", "CohereForCausalLM", {"logit_scale": 0.0625, "layer_norm_eps": 1e-5, "use_qk_norm": False, "tie_word_embeddings": True}),
@@ -105,7 +109,7 @@ def test_converted_model_matches_hf_forward(tmp_path, family):
     with torch.no_grad():
         want = model(torch.tensor([ids])).logits[0]
     ref = ReferenceModel.from_gguf(out)
-    assert ref.cfg.arch == ("llama" if family in ("llama", "llama31", "mistral", "mixtral") else family if family in ("command-r", "ernie4_5-moe") else family.split("-")[0])
+    assert ref.cfg.arch == ("llama" if family in ("llama", "llama31", "mistral", "mixtral") else family if family in ("command-r", "ernie4_5-moe", "minimax-m2") else family.split("-")[0])
     if family == "qwen2-yarn":
         assert ref.cfg.yarn_factor == 4.0 and ref.cfg.yarn_orig_ctx == 128
     if family == "llama31":

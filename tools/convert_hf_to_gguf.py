@@ -28,7 +28,7 @@ ARCHS = {"LlamaForCausalLM": "llama", "MistralForCausalLM": "llama", "MixtralFor
          "Starcoder2ForCausalLM": "starcoder2", "FalconForCausalLM": "falcon", "OlmoForCausalLM": "olmo", "CohereForCausalLM": "command-r",
          "GPTNeoXForCausalLM": "gptneox", "StableLmForCausalLM": "stablelm", "NemotronForCausalLM": "nemotron", "ArceeForCausalLM": "arcee",
          "GPT2LMHeadModel": "gpt2", "GPTBigCodeForCausalLM": "starcoder", "Olmo2ForCausalLM": "olmo2", "Glm4ForCausalLM": "glm4", "PhiForCausalLM": "phi2", "OlmoeForCausalLM": "olmoe", "Glm4MoeForCausalLM": "glm4moe", "Dots1ForCausalLM": "dots1",
-         "Ernie4_5_MoeForCausalLM": "ernie4_5-moe"}
+         "Ernie4_5_MoeForCausalLM": "ernie4_5-moe", "MiniMaxM2ForCausalLM": "minimax-m2", "Exaone4ForCausalLM": "exaone4"}
 # families whose GGUF graph rotates adjacent pairs: HF's half-split Q/K rows are permuted on the way in (ernie4_5 already stores
 # adjacent pairs upstream, so it is not in the list)
 PERMUTE_QK = ("llama", "granite", "granitemoe", "smollm3", "olmo", "arcee")
@@ -196,6 +196,9 @@ def convert(src: str, dst: str, outtype: str = "F16") -> str:
             w.add(f"{a}.interleave_moe_layer_step", 1, ValueType.UINT32)
             if cfg.get("moe_num_shared_experts"):
                 w.add(f"{a}.expert_shared_feed_forward_length", int(cfg["moe_num_shared_experts"]) * int(cfg["moe_intermediate_size"]), ValueType.UINT32)
+        if a == "minimax-m2":
+            w.add(f"{a}.expert_gating_func", 2, ValueType.UINT32)      # sigmoid scores, selection bias, renormalised weights
+            w.add(f"{a}.expert_feed_forward_length", int(cfg["intermediate_size"]), ValueType.UINT32)
         if a in ("glm4moe", "dots1"):      # DeepSeek-V3 style routing: sigmoid scores, selection bias, scaled weights, dense lead layers, ungated shared experts
             w.add(f"{a}.expert_shared_count", int(cfg.get("n_shared_experts", 1)), ValueType.UINT32)
             w.add(f"{a}.leading_dense_block_count", int(cfg.get("first_k_dense_replace", 0)), ValueType.UINT32)
@@ -215,8 +218,8 @@ def convert(src: str, dst: str, outtype: str = "F16") -> str:
     else:
         w.add(f"{a}.attention.layer_norm_rms_epsilon", float(cfg.get("rms_norm_eps", 1e-5)), ValueType.FLOAT32)
     w.add(f"{a}.rope.freq_base", theta, ValueType.FLOAT32)
-    rot = (cfg.get("rotary_pct") or cfg.get("partial_rotary_factor") or rope.get("partial_rotary_factor")) if a in ("gptneox", "stablelm", "nemotron", "glm4", "phi2", "glm4moe") else None
-    w.add(f"{a}.rope.dimension_count", int(D * float(rot)) if rot else D, ValueType.UINT32)
+    rot = (cfg.get("rotary_pct") or cfg.get("partial_rotary_factor") or rope.get("partial_rotary_factor")) if a in ("gptneox", "stablelm", "nemotron", "glm4", "phi2", "glm4moe", "minimax-m2") else None
+    w.add(f"{a}.rope.dimension_count", int(D * float(rot)) if rot else int(cfg["rotary_dim"]) if (a == "minimax-m2" and cfg.get("rotary_dim")) else D, ValueType.UINT32)
     if a == "gptneox":
         w.add(f"{a}.use_parallel_residual", bool(cfg.get("use_parallel_residual", True)))
     if D * H != E:
@@ -264,7 +267,7 @@ def convert(src: str, dst: str, outtype: str = "F16") -> str:
         t = tensors[name]
         if rest.startswith("shared_experts."):       # glm4moe: always-on experts, no gate
             tensors[f"__moe__.blk.{il}.ffn_{rest.split('.')[1].split('_')[0]}_shexp.weight"] = tensors.pop(name)
-        elif rest in ("gate.e_score_correction_bias", "gate.moe_statics.e_score_correction_bias", "moe_statics.e_score_correction_bias"):
+        elif rest in ("gate.e_score_correction_bias", "gate.moe_statics.e_score_correction_bias", "moe_statics.e_score_correction_bias", "e_score_correction_bias"):
             tensors[f"__moe__.blk.{il}.exp_probs_b.bias"] = tensors.pop(name).reshape(-1)
         elif rest.startswith("shared_expert"):
             sh = {"shared_expert_gate.weight": "ffn_gate_inp_shexp.weight", "shared_expert.gate_proj.weight": "ffn_gate_shexp.weight",
@@ -338,7 +341,7 @@ def convert(src: str, dst: str, outtype: str = "F16") -> str:
             # HF interleaves per head [q_h | k_h | v_h]; GGUF wants [all Q | all K | all V] (weight rows and bias entries alike)
             g = t.reshape(H, 3, D, *t.shape[1:])
             t = np.concatenate([g[:, 0].reshape(H * D, *t.shape[1:]), g[:, 1].reshape(H * D, *t.shape[1:]), g[:, 2].reshape(H * D, *t.shape[1:])], 0)
-        if a == "olmo2":        # no pre-norms: HF's two layer norms are the post-branch ones
+        if a in ("olmo2", "exaone4"):        # no pre-norms: HF's two layer norms are the post-branch ones
             out = out.replace("ffn_norm.weight", "post_attention_norm.weight")
         if a == "nemotron" and out.endswith("_norm.weight"):
             t = t + 1.0          # LayerNorm1p: the checkpoint stores weight - 1
