@@ -258,18 +258,21 @@ def write_synthetic_gguf(path: str, cfg: ModelConfig, ftype: str = "F16", seed: 
             w.add(f"{a}.expert_feed_forward_length", cfg.n_ff, ValueType.UINT32)
         w.add(f"{a}.expert_count", cfg.n_expert, ValueType.UINT32)
         w.add(f"{a}.expert_used_count", cfg.n_expert_used, ValueType.UINT32)
+        if cfg.n_expert_groups > 1:
+            w.add(f"{a}.expert_group_count", cfg.n_expert_groups, ValueType.UINT32)
+            w.add(f"{a}.expert_group_used_count", cfg.n_group_used, ValueType.UINT32)
         if cfg.n_ff_shared and a not in ("deepseek", "bailingmoe", "glm4moe", "dots1"):
             w.add(f"{a}.expert_shared_feed_forward_length", cfg.n_ff_shared, ValueType.UINT32)
         if a == "ernie4_5-moe":
             w.add(f"{a}.leading_dense_block_count", cfg.n_layer_dense_lead, ValueType.UINT32)
             w.add(f"{a}.interleave_moe_layer_step", cfg.moe_layer_step, ValueType.UINT32)
-        if a in ("deepseek", "bailingmoe", "glm4moe", "dots1"):
+        if a in ("deepseek", "bailingmoe", "glm4moe", "dots1", "bailingmoe2"):
             w.add(f"{a}.leading_dense_block_count", cfg.n_layer_dense_lead, ValueType.UINT32)
             w.add(f"{a}.expert_shared_count", cfg.n_ff_shared // cfg.n_ff, ValueType.UINT32)
             w.add(f"{a}.expert_weights_scale", float(cfg.expert_weights_scale), ValueType.FLOAT32)
-            if a in ("bailingmoe", "glm4moe", "dots1"):
+            if a in ("bailingmoe", "glm4moe", "dots1", "bailingmoe2"):
                 w.add(f"{a}.expert_weights_norm", bool(cfg.moe_norm_topk))
-        if a in ("glm4moe", "dots1", "minimax-m2"):
+        if a in ("glm4moe", "dots1", "minimax-m2", "bailingmoe2"):
             w.add(f"{a}.expert_gating_func", 2 if cfg.moe_gating == "sigmoid" else 1, ValueType.UINT32)
     if vocab:
         toks, scores, types = synthetic_vocab(cfg.vocab_size)

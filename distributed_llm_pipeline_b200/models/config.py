@@ -62,6 +62,8 @@ class ModelConfig:
     moe_gating: str = "softmax"    # "softmax" | "sigmoid"
     moe_sel_bias: bool = False     # `blk.N.exp_probs_b.bias`
     moe_scale_w: bool = False
+    n_expert_groups: int = 0       # > 1: experts are picked from the n_group_used best groups only (group score = its two best experts; bailingmoe2)
+    n_group_used: int = 0
     # LayerNorm / GELU / parallel-residual families (starcoder2, falcon, olmo, orion, command-r): the generic layer path
     norm_type: str = "rms"         # "rms" | "layer" (mean-centred; weight and bias optional per file: olmo has neither)
     ffn_act: str = "swiglu"        # "swiglu" (gated SiLU) | "gelu" | "relu2" (non-gated: ffn_up -> activation -> ffn_down, biases optional)
@@ -257,6 +259,10 @@ PRESETS: dict[str, ModelConfig] = {
     "tiny-minimax-m2": ModelConfig(name="tiny-minimax-m2", arch="minimax-m2", vocab_size=512, n_embd=256, n_layer=2, n_head=4, n_head_kv=2, head_dim=64, n_ff=256,
                                    n_ctx_train=512, rope_theta=10000.0, rope_dim=32, rope_neox=True, qk_norm_full=True, n_expert=4, n_expert_used=2,
                                    moe_norm_topk=True, moe_gating="sigmoid", moe_sel_bias=True),
+    "tiny-bailingmoe2": ModelConfig(name="tiny-bailingmoe2", arch="bailingmoe2", vocab_size=512, n_embd=256, n_layer=3, n_head=4, n_head_kv=2, head_dim=64,
+                                    n_ff=256, n_ctx_train=512, rope_theta=10000.0, rope_dim=32, rope_neox=True, fused_qkv=True, qk_norm=True, n_expert=8,
+                                    n_expert_used=2, moe_norm_topk=True, n_ff_shared=256, n_layer_dense_lead=1, n_ff_dense=512, expert_weights_scale=2.5,
+                                    moe_gating="sigmoid", moe_sel_bias=True, moe_scale_w=True, n_expert_groups=4, n_group_used=2),
     "tiny-exaone4": ModelConfig(name="tiny-exaone4", arch="exaone4", vocab_size=512, n_embd=256, n_layer=2, n_head=4, n_head_kv=2, head_dim=64, n_ff=512,
                                 n_ctx_train=512, rope_theta=10000.0, rope_dim=64, rope_neox=True, qk_norm=True, post_norm=True, pre_norm=False),
     "tiny-command-r": ModelConfig(name="tiny-command-r", arch="command-r", vocab_size=512, n_embd=256, n_layer=2, n_head=4, n_head_kv=2,
@@ -298,7 +304,7 @@ PRESETS: dict[str, ModelConfig] = {
 SUPPORTED_ARCHS = {"llama", "qwen2", "qwen2moe", "qwen3", "qwen3moe", "phi3", "granite",
                    "internlm2", "xverse", "ernie4_5", "exaone", "seed_oss", "minicpm", "granitemoe", "smollm3",
                    "starcoder2", "falcon", "olmo", "orion", "command-r", "gptneox", "stablelm", "nemotron", "arcee",
-                   "gpt2", "starcoder", "codeshell", "qwen", "baichuan", "olmo2", "glm4", "mistral3", "pangu-embedded", "chatglm", "plamo", "deepseek", "bailingmoe", "qwen2vl", "qwen3vl", "exaone4", "phi2", "olmoe", "qwen3vlmoe", "glm4moe", "dots1", "ernie4_5-moe", "minimax-m2"}
+                   "gpt2", "starcoder", "codeshell", "qwen", "baichuan", "olmo2", "glm4", "mistral3", "pangu-embedded", "chatglm", "plamo", "deepseek", "bailingmoe", "qwen2vl", "qwen3vl", "exaone4", "phi2", "olmoe", "qwen3vlmoe", "glm4moe", "dots1", "ernie4_5-moe", "minimax-m2", "bailingmoe2"}
 ROPE_NORM_ARCHS = {"llama", "granite", "granitemoe", "minicpm", "internlm2", "xverse", "ernie4_5", "ernie4_5-moe", "smollm3", "olmo", "command-r", "arcee", "baichuan", "glm4", "mistral3", "chatglm", "deepseek", "bailingmoe"}     # llama_model_rope_type
 # LayerNorm families and what differs beyond the norm (llama.cpp/src/models/{starcoder2,falcon,olmo,orion,command-r}.cpp):
 #   starcoder2: biases on every matrix, non-gated GELU MLP;  falcon: fused QKV, GELU MLP, attention and MLP in parallel from the same
@@ -378,11 +384,13 @@ def config_from_gguf(meta: dict[str, Any], tensors: dict | None = None) -> Model
         embedding_scale=float(g("embedding_scale") or dflt["embedding_scale"]), residual_scale=float(g("residual_scale") or dflt["residual_scale"]),
         logit_scale=(1.0 / float(g("logit_scale") or 1.0)) if arch == "command-r" else float(g("logit_scale") or dflt["logit_scale"]), attention_scale=float(g("attention.scale", 0.0) or 0.0),
         no_rope_step=4 if arch == "smollm3" else 1 if arch in LEARNED_POS_ARCHS else 0, learned_pos=arch in LEARNED_POS_ARCHS,
-        moe_gating="sigmoid" if ((arch == "glm4moe" and int(g("expert_gating_func", 0) or 0) in (0, 2)) or (arch in ("dots1", "minimax-m2") and int(g("expert_gating_func", 0) or 0) == 2)) else "softmax",
-        moe_sel_bias=tensors is not None and any(k.endswith(".exp_probs_b.bias") for k in tensors), moe_scale_w=arch in ("glm4moe", "dots1"),
+        moe_gating="sigmoid" if ((arch == "glm4moe" and int(g("expert_gating_func", 0) or 0) in (0, 2)) or (arch in ("dots1", "minimax-m2", "bailingmoe2") and int(g("expert_gating_func", 0) or 0) == 2)) else "softmax",
+        moe_sel_bias=tensors is not None and any(k.endswith(".exp_probs_b.bias") for k in tensors), moe_scale_w=arch in ("glm4moe", "dots1", "bailingmoe2"),
+        n_expert_groups=int(g("expert_group_count", 0) or 0), n_group_used=int(g("expert_group_used_count", 0) or 0),
         moe_layer_step=int(g("interleave_moe_layer_step", 1) or 1),
-        moe_norm_topk=bool(g("expert_weights_norm", False)) if arch in ("bailingmoe", "glm4moe", "dots1") else arch not in ("qwen2moe", "deepseek", "olmoe"),
-        n_ff_shared=int(g("expert_shared_feed_forward_length", 0) or 0) or (int(g("expert_shared_count", 0) or 0) * int(g("expert_feed_forward_length", 0) or 0)),
+        moe_norm_topk=bool(g("expert_weights_norm", False)) if arch in ("bailingmoe", "glm4moe", "dots1", "bailingmoe2") else arch not in ("qwen2moe", "deepseek", "olmoe"),
+        n_ff_shared=(int(g("expert_shared_feed_forward_length", 0) or g("expert_feed_forward_length")) * int(g("expert_shared_count", 1) or 1)) if arch == "bailingmoe2" else
+        int(g("expert_shared_feed_forward_length", 0) or 0) or (int(g("expert_shared_count", 0) or 0) * int(g("expert_feed_forward_length", 0) or 0)),
         n_layer_dense_lead=int(g("leading_dense_block_count", 0) or 0), expert_weights_scale=float(g("expert_weights_scale", 1.0) or 1.0),
         n_ff_dense=int(g("feed_forward_length")) if (int(g("leading_dense_block_count", 0) or 0) > 0 or int(g("interleave_moe_layer_step", 1) or 1) > 1) else 0,
         qkv_bias=arch in ("qwen2", "qwen2moe", "qwen2vl") or (tensors is not None and ("blk.0.attn_q.bias" in tensors or "blk.0.attn_qkv.bias" in tensors)),

@@ -21,7 +21,7 @@ import torch
 
 from ..ops import api as ops
 from .config import ModelConfig
-from .reference import rope_attn_scale, rope_inv_freq
+from .reference import limit_to_groups, rope_attn_scale, rope_inv_freq
 from .weights import ModelWeights
 
 
@@ -449,7 +449,7 @@ class LlamaEngine:
         h = self.h[:T]
         if (T <= 4 and lw.e_gate_s is not None and cfg.n_expert <= 32 and cfg.n_embd % 256 == 0 and self.F % 256 == 0
                 and lw.router_w.N % 2 == 0 and cfg.moe_norm_topk and not cfg.n_ff_shared and self.device.type == "cuda"
-                and cfg.moe_gating == "softmax" and lw.sel_bias is None
+                and cfg.moe_gating == "softmax" and lw.sel_bias is None and cfg.n_expert_groups <= 1
                 and os.environ.get("DLP_MOE_GEMV", "1") == "1"):
             return self._moe_device(lw, T)
         if xn is None:
@@ -459,11 +459,9 @@ class LlamaEngine:
         # host-routed fallback (CPU engine, mixed expert types): not graph-capturable
         logits = xn.float() @ lw.router.T
         probs = torch.sigmoid(logits) if cfg.moe_gating == "sigmoid" else torch.softmax(logits, -1)
-        if lw.sel_bias is not None:       # DeepSeek-V3 style: the bias picks the experts, the unbiased scores weigh them
-            topi = (probs + lw.sel_bias).topk(cfg.n_expert_used, -1).indices
-            topw = probs.gather(-1, topi)
-        else:
-            topw, topi = probs.topk(cfg.n_expert_used, -1)
+        sel = probs + lw.sel_bias if lw.sel_bias is not None else probs      # DeepSeek-V3 style: the bias picks the experts, the unbiased scores weigh them
+        topi = limit_to_groups(sel, cfg.n_expert_groups, cfg.n_group_used).topk(cfg.n_expert_used, -1).indices
+        topw = probs.gather(-1, topi)
         if cfg.moe_norm_topk:
             topw = topw / topw.sum(-1, keepdim=True).clamp_min(6.103515625e-5)
         out = torch.zeros(T, self.E, dtype=torch.float32, device=h.device)
@@ -486,7 +484,7 @@ class LlamaEngine:
     def _moe_grouped_ok(self, lw) -> bool:
         cfg = self.cfg
         return (self.device.type == "cuda" and lw.e_gate_s is not None and lw.router_wp is not None and cfg.n_expert <= 256
-                and cfg.moe_gating == "softmax" and lw.sel_bias is None      # (the device router implements softmax top-k only)
+                and cfg.moe_gating == "softmax" and lw.sel_bias is None and cfg.n_expert_groups <= 1     # (the device router implements softmax top-k only)
                 and cfg.n_expert_used <= 32 and not ops.TWO_PASS_DEQUANT and os.environ.get("DLP_MOE_GROUPED", "1") == "1")
 
     def _moe_grouped(self, lw, T: int, xn):

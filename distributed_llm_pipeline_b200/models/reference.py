@@ -82,6 +82,17 @@ class RefKVCache:
     length: int = 0
 
 
+def limit_to_groups(sel: torch.Tensor, n_groups: int, n_used: int) -> torch.Tensor:
+    """Group-limited expert selection (DeepSeek-V3 / bailingmoe2; llama-graph.cpp:1075-1098): the experts form `n_groups` equal groups, a
+    group scores the sum of its two best selection scores, and only experts of the `n_used` best groups stay eligible."""
+    if n_groups <= 1:
+        return sel
+    g = sel.reshape(*sel.shape[:-1], n_groups, -1)
+    keep = g.topk(2, dim=-1).values.sum(-1).topk(n_used, dim=-1).indices
+    mask = torch.zeros(g.shape[:-1], dtype=torch.bool, device=sel.device).scatter_(-1, keep, True)
+    return g.masked_fill(~mask[..., None], float("-inf")).reshape(sel.shape)
+
+
 class ReferenceModel:
     """Dense fp32 weights + eager forward.  Small models only (it dequantises everything)."""
 
@@ -188,11 +199,10 @@ class ReferenceModel:
             return self.mm(torch.nn.functional.silu(g) * u, p + "ffn_down.weight")
         logits = self.mm(x, p + "ffn_gate_inp.weight")
         probs = torch.sigmoid(logits) if c.moe_gating == "sigmoid" else torch.softmax(logits, dim=-1)
-        if p + "exp_probs_b.bias" in w:      # the bias steers which experts are picked; their weights are the unbiased scores
-            topi = (probs + w[p + "exp_probs_b.bias"]).topk(c.n_expert_used, dim=-1).indices
-            topw = probs.gather(-1, topi)
-        else:
-            topw, topi = probs.topk(c.n_expert_used, dim=-1)
+        sel = probs + w[p + "exp_probs_b.bias"] if p + "exp_probs_b.bias" in w else probs     # the bias steers which experts are picked ...
+        sel = limit_to_groups(sel, c.n_expert_groups, c.n_group_used)
+        topi = sel.topk(c.n_expert_used, dim=-1).indices
+        topw = probs.gather(-1, topi)                                                          # ... their weights are the unbiased scores
         if c.moe_norm_topk:
             topw = topw / topw.sum(-1, keepdim=True).clamp_min(6.103515625e-5)
         if c.moe_scale_w:
