@@ -47,15 +47,21 @@ PRE_TOKENIZERS: dict[str, list[str]] = {
     "tekken": [r"[^\r\n\p{L}\p{N}]?((?=[\p{L}])([^a-z]))*((?=[\p{L}])([^A-Z]))+|[^\r\n\p{L}\p{N}]?((?=[\p{L}])([^a-z]))+((?=[\p{L}])([^A-Z]))*|\p{N}| ?[^\s\p{L}\p{N}]+[\r\n/]*|\s*[\r\n]+|\s+(?!\S)|\s+"],
     "gpt-4o": [r"[^\r\n\p{L}\p{N}]?((?=[\p{L}])([^a-z]))*((?=[\p{L}])([^A-Z]))+" + _CONTR + r"?|[^\r\n\p{L}\p{N}]?((?=[\p{L}])([^a-z]))+((?=[\p{L}])([^A-Z]))*" + _CONTR
                + r"?|\p{N}{1,3}| ?[^\s\p{L}\p{N}]+[\r\n/]*|\s*[\r\n]+|\s+(?!\S)|\s+"],
+    "bailingmoe": [r"'(?:[sSdDmMtT]|[lL][lL]|[vV][eE]|[rR][eE])|[^\r\n\p{L}\p{N}]?\p{L}+|\p{N}| ?[^\s\p{L}\p{N}]+[\r\n]*|\s*[\r\n]|\s+(?!\S)|\s+"],
+    "exaone-moe": [_CONTR + r"|[^\r\n\p{L}\p{N}]?(?:\p{L}\p{M}*(?: \p{L}\p{M}*)*)+|\p{N}| ?[^\s\p{L}\p{N}]+[\r\n/]?|\s*[\r\n]|\s+(?!\S)|\s+"],
+    "chameleon": ["<sentinel:[0-9]+>", "(IMGIMG)((A|B|C|D|E|F|G|H|I){1,4})Z", r"([\t\n]|    |  )", r"\p{N}", r"[\p{P}!-/:-@\[-`{-~]", _GPT2_CORE],
 }
-for _name, _same in (("llama3", "llama-bpe"), ("llama-v3", "llama-bpe"), ("dbrx", "llama-bpe"), ("smaug-bpe", "llama-bpe"),
+for _name, _same in (("llama3", "llama-bpe"), ("falcon3", "llama-bpe"), ("falcon-h1", "llama-bpe"), ("pixtral", "llama-bpe"), ("midm-2.0", "llama-bpe"), ("lfm2", "llama-bpe"),
+                     ("jina-es", "gpt-2"), ("jina-de", "gpt-2"), ("jina-v1-en", "gpt-2"), ("jina-v2-es", "gpt-2"), ("jina-v2-de", "gpt-2"), ("jina-v2-code", "gpt-2"),
+                     ("a.x-4.0", "gpt-2"), ("mellum", "gpt-2"), ("modern-bert", "gpt-2"), ("trillion", "gpt-2"), ("granite-docling", "gpt-2"),
+                     ("kormo", "qwen2"), ("solar-open", "qwen2"), ("bailingmoe2", "bailingmoe"), ("llada-moe", "bailingmoe"), ("llama-v3", "llama-bpe"), ("dbrx", "llama-bpe"), ("smaug-bpe", "llama-bpe"),
                      ("mpt", "gpt-2"), ("olmo", "gpt-2"), ("jais", "gpt-2"), ("phi-2", "gpt-2"), ("exaone4", "gpt-2"), ("roberta-bpe", "gpt-2"), ("gigachat", "gpt-2"),
                      ("stablelm2", "qwen2"), ("deepseek-r1-qwen", "qwen2"), ("hunyuan", "qwen2"), ("megrez", "qwen2"), ("grok-2", "qwen2"),
                      ("glm4", "chatglm-bpe"), ("refact", "starcoder"), ("command-r", "starcoder"), ("smollm", "starcoder"), ("codeshell", "starcoder"),
                      ("exaone", "starcoder"), ("minerva-7b", "starcoder"), ("poro-chat", "bloom"), ("gpt3-finnish", "bloom"), ("llama4", "gpt-4o"),
                      ("minimax-m2", "gpt-4o"), ("deepseek3-llm", "deepseek-v3"), ("hunyuan-dense", "deepseek-v3")):
     PRE_TOKENIZERS[_name] = PRE_TOKENIZERS[_same]
-IGNORE_MERGES = {"llama-bpe", "llama3", "llama-v3", "tekken"}       # a word that is itself a token is taken whole (llama-vocab.cpp `ignore_merges`)
+IGNORE_MERGES = {"llama-bpe", "llama3", "llama-v3", "tekken", "falcon3", "falcon-h1", "pixtral", "midm-2.0", "lfm2"}       # a word that is itself a token is taken whole (llama-vocab.cpp `ignore_merges`)
 
 
 def pre_split(text: str, exprs) -> list[str]:

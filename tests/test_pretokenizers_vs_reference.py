@@ -90,7 +90,8 @@ def with_vocab(base: str, dst: str, toks, merges, pre: str) -> str:
 
 
 NAMES = ["gpt-2", "llama-bpe", "qwen2", "starcoder", "falcon", "deepseek-coder", "deepseek-v3", "chatglm-bpe", "tekken", "gpt-4o", "bloom", "viking",
-         "seed-coder", "command-r", "smollm", "olmo", "stablelm2", "refact", "mpt"]
+         "seed-coder", "command-r", "smollm", "olmo", "stablelm2", "refact", "mpt", "bailingmoe2", "exaone-moe", "chameleon", "falcon3", "kormo",
+         "trillion", "jina-v2-code", "solar-open"]
 
 
 @pytest.mark.parametrize("pre", NAMES)
