@@ -124,8 +124,10 @@ class Tokenizer:
                 self.add_bos = bool(meta.get("tokenizer.ggml.add_bos_token", True))      # [CLS] ... [SEP]
                 self.sep_id = int(meta.get("tokenizer.ggml.seperator_token_id", meta.get("tokenizer.ggml.eos_token_id", self.eos_id)))
             elif self.model == "t5":
+                cm = meta.get("tokenizer.ggml.precompiled_charsmap")
                 self.codec = UgmCodec(self.tokens, self.scores, self.types, self.unk_id, self.add_space_prefix,
-                                      bool(meta.get("tokenizer.ggml.remove_extra_whitespaces", True)))
+                                      bool(meta.get("tokenizer.ggml.remove_extra_whitespaces", True)),
+                                      charsmap=bytes(bytearray(int(x) & 0xFF for x in cm)) if cm is not None and len(cm) else None)
                 self.add_bos = bool(meta.get("tokenizer.ggml.add_bos_token", False))
             else:
                 self.codec = RwkvCodec(self.tokens, self.unk_id)

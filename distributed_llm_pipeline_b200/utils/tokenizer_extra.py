@@ -76,16 +76,98 @@ class WpmCodec:
         return self.tokens[tid].replace(SPACE, " ").encode("utf-8")
 
 
+class CharsMap:
+    """SentencePiece's precompiled normalisation table (`tokenizer.ggml.precompiled_charsmap`): a 4-byte length, a double-array trie of that
+    many bytes whose keys are UTF-8 byte strings, then the replacement strings, NUL-terminated.  Each trie unit is a packed uint32 -
+    child check byte in bits 0-7, "has a value" in bit 8, the XOR offset to the children in bits 10-30 (shifted by 8 more when bit 9 is set);
+    the value unit behind a key holds the byte offset of its replacement (llama-vocab.cpp:1010-1050, :1069-1114).  `apply` rewrites a text by
+    always taking the longest key that matches at the current byte; bytes that are not valid UTF-8 become U+FFFD."""
+
+    def __init__(self, blob: bytes):
+        import struct
+        n = struct.unpack_from("<I", blob, 0)[0]
+        if 4 + n >= len(blob) or n % 4:
+            raise ValueError("precompiled_charsmap: the trie does not fit the blob")
+        self.units = struct.unpack_from(f"<{n // 4}I", blob, 4)
+        self.repl = blob[4 + n:]
+
+    @staticmethod
+    def _offset(u: int) -> int:
+        return (u >> 10) << ((u & 0x200) >> 6)
+
+    def longest(self, data: bytes, pos: int) -> tuple[int, bytes | None]:
+        """(bytes consumed, replacement) for the longest key matching data[pos:], or (0, None)."""
+        units, node = self.units, 0
+        node ^= self._offset(units[0])
+        best_len, best_val = 0, -1
+        for i in range(pos, len(data)):
+            c = data[i]
+            if c == 0:
+                break
+            node ^= c
+            if node >= len(units) or (units[node] & 0x800000FF) != c:
+                break
+            u = units[node]
+            node ^= self._offset(u)
+            if (u >> 8) & 1:
+                best_len, best_val = i - pos + 1, units[node] & 0x7FFFFFFF
+        if best_len == 0:
+            return 0, None
+        end = self.repl.index(b"\0", best_val)
+        return best_len, self.repl[best_val:end]
+
+    def apply(self, text: str, keep: "dict | None" = None) -> str:
+        data, out, pos = text.encode("utf-8"), bytearray(), 0
+        while pos < len(data):
+            if keep is not None:            # user-defined tokens pass through untouched (trie of their UTF-8 bytes)
+                node, j, hit = keep, pos, 0
+                while j < len(data) and data[j] in node:
+                    node = node[data[j]]
+                    j += 1
+                    if None in node:
+                        hit = j - pos
+                if hit:
+                    out += data[pos:pos + hit]
+                    pos += hit
+                    continue
+            n, rep = self.longest(data, pos)
+            if n:
+                out += rep
+                pos += n
+                continue
+            b0 = data[pos]
+            width = 1 if b0 < 0x80 else 2 if 0xC0 <= b0 < 0xE0 else 3 if 0xE0 <= b0 < 0xF0 else 4 if 0xF0 <= b0 < 0xF8 else 0
+            chunk = data[pos:pos + width]
+            try:
+                if width == 0 or len(chunk) < width:
+                    raise UnicodeDecodeError("utf-8", bytes(chunk), 0, 1, "truncated")
+                chunk.decode("utf-8")
+                out += chunk
+                pos += width
+            except UnicodeDecodeError:
+                out += b"\xef\xbf\xbd"
+                pos += 1
+        return out.decode("utf-8", errors="replace")
+
+
 class UgmCodec:
     """Unigram language-model segmentation (SentencePiece / T5): the split of the normalised text that maximises the sum of token
     scores, found by a forward Viterbi pass over a prefix trie.  Characters no token covers cost `min_score - 10` and map to UNK;
-    user-defined tokens match with score 0.  Normalisation: NFKC stands in for the SentencePiece `nmt_nfkc` character map (the
-    reference reads the model's `precompiled_charsmap`; for text without compatibility characters both are the identity), then
+    user-defined tokens match with score 0.  Normalisation: the model's own `precompiled_charsmap` (`CharsMap`) when the file carries one,
+    else NFKC (for text without compatibility characters both are the identity), then
     runs of spaces collapse (`remove_extra_whitespaces`), a space is prefixed (`add_space_prefix`) and spaces become U+2581."""
 
     def __init__(self, tokens: list[str], scores: list[float], types: list[int], unk_id: int, add_space_prefix: bool = True,
-                 remove_extra_whitespaces: bool = True):
+                 remove_extra_whitespaces: bool = True, charsmap: bytes | None = None):
         self.tokens, self.types, self.unk_id = tokens, types, unk_id
+        self.charsmap = CharsMap(charsmap) if charsmap else None
+        self.user_trie: dict = {}
+        for t, typ in zip(tokens, types):
+            if typ == TokenType.USER_DEFINED and t:
+                node = self.user_trie
+                for byte in t.encode("utf-8"):
+                    node = node.setdefault(byte, {})
+                node[None] = True
         self.add_space_prefix, self.remove_extra_ws = add_space_prefix, remove_extra_whitespaces
         self.trie: dict = {}
         normal = [s for s, t in zip(scores, types) if t == TokenType.NORMAL]
@@ -100,7 +182,7 @@ class UgmCodec:
             node[None] = (tid, 0.0 if typ == TokenType.USER_DEFINED else float(scores[tid]))
 
     def normalize(self, text: str) -> str:
-        s = unicodedata.normalize("NFKC", text)
+        s = self.charsmap.apply(text, self.user_trie or None) if self.charsmap is not None else unicodedata.normalize("NFKC", text)
         if self.remove_extra_ws:
             s = " ".join(p for p in s.split(" ") if p) if s.strip(" ") else ""
         if self.add_space_prefix and s:

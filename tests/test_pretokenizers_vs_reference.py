@@ -112,8 +112,9 @@ def test_bpe_pretokenizer_matches_reference(setup, pre):
     assert mine[:len(ref_ids)] == ref_ids, next((i, mine[i - 3:i + 3], ref_ids[i - 3:i + 3]) for i in range(len(ref_ids)) if mine[i] != ref_ids[i])
 
 
-def _ref_tokens(setup, model, name):
-    scratch, env, _, _, _, text_path = setup
+def _ref_tokens(setup, model, name, text_path=None):
+    scratch, env = setup[0], setup[1]
+    text_path = text_path or setup[5]
     out = os.path.join(scratch, f"{name}.logits")
     p = subprocess.run([ref_build.exe("llama-perplexity"), "-m", model, "-f", text_path, "-c", "32", "-b", "32", "--chunks", "1000", "-ngl", "0", "-t", "4",
                         "--save-all-logits", out], env=env, capture_output=True, text=True, timeout=600)
@@ -188,6 +189,41 @@ def test_unigram_vocab_matches_reference(setup):
     model = _model_with(setup, "ugm", meta, len(pieces))
     ref_ids = _ref_tokens(setup, model, "ugm")
     mine = Tokenizer(open_gguf(model).metadata).encode(TEXT)
+    assert len(ref_ids) > 200 and mine[:len(ref_ids)] == ref_ids, next((i, mine[max(0, i - 3):i + 3], ref_ids[max(0, i - 3):i + 3]) for i in range(len(ref_ids)) if mine[i] != ref_ids[i])
+
+
+def test_unigram_with_precompiled_charsmap_matches_reference(setup):
+    """A sentencepiece-trained unigram model with its `precompiled_charsmap` in the file: the reference normalises through the double-array
+    trie (llama-vocab.cpp:1057-1126) and so must `CharsMap`; the text is full of compatibility characters and has a user-defined symbol."""
+    spm = pytest.importorskip("sentencepiece")
+    from sentencepiece import sentencepiece_model_pb2 as pb
+    scratch = setup[0]
+    corpus = os.path.join(scratch, "ugm-corpus.txt")
+    open(corpus, "w").write(TEXT.replace("你好世界 こんにちは ", ""))
+    prefix = os.path.join(scratch, "ugmcm")
+    spm.SentencePieceTrainer.train(input=corpus, model_prefix=prefix, vocab_size=150, model_type="unigram", character_coverage=1.0, bos_id=-1, eos_id=1,
+                                   unk_id=2, pad_id=0, hard_vocab_limit=False, minloglevel=2, user_defined_symbols=["<ｘ>"])
+    sp = spm.SentencePieceProcessor(model_file=prefix + ".model")
+    proto = pb.ModelProto()
+    proto.ParseFromString(open(prefix + ".model", "rb").read())
+    n = sp.get_piece_size()
+    types = [int(TokenType.CONTROL) if sp.is_control(i) else int(TokenType.UNKNOWN) if sp.is_unknown(i) else
+             int(TokenType.USER_DEFINED) if proto.pieces[i].type == 4 else int(TokenType.NORMAL) for i in range(n)]
+    meta = {"tokenizer.ggml.model": ("t5", {}), "tokenizer.ggml.tokens": ([sp.id_to_piece(i) for i in range(n)], {"etype": ValueType.STRING}),
+            "tokenizer.ggml.scores": (np.asarray([sp.get_score(i) for i in range(n)], np.float32), {"etype": ValueType.FLOAT32}),
+            "tokenizer.ggml.token_type": (np.asarray(types, np.int32), {"etype": ValueType.INT32}),
+            "tokenizer.ggml.unknown_token_id": (2, {"vtype": ValueType.UINT32}), "tokenizer.ggml.eos_token_id": (1, {"vtype": ValueType.UINT32}),
+            "tokenizer.ggml.padding_token_id": (0, {"vtype": ValueType.UINT32}), "tokenizer.ggml.add_bos_token": (False, {}),
+            "tokenizer.ggml.add_eos_token": (False, {}), "tokenizer.ggml.add_space_prefix": (True, {}), "tokenizer.ggml.remove_extra_whitespaces": (True, {}),
+            "tokenizer.ggml.precompiled_charsmap": (np.frombuffer(proto.normalizer_spec.precompiled_charsmap, np.uint8), {"etype": ValueType.UINT8})}
+    model = _model_with(setup, "ugmcm", meta, n)
+    text = ("Ｈｅｌｌｏ ｗｏｒｌｄ ﬁne ① ２３ Ⅷ tests <ｘ> we'll see\u3000Two\u200bspaces ｶﾞ ㌔ CamelCaseWords e-mail@example.com ... end\n") * 24
+    text_path = os.path.join(scratch, "ugmcm-text.txt")
+    open(text_path, "w", encoding="utf-8").write(text)
+    ref_ids = _ref_tokens(setup, model, "ugmcm", text_path)
+    tok = Tokenizer(open_gguf(model).metadata)
+    assert tok.codec.charsmap is not None
+    mine = tok.encode(text)
     assert len(ref_ids) > 200 and mine[:len(ref_ids)] == ref_ids, next((i, mine[max(0, i - 3):i + 3], ref_ids[max(0, i - 3):i + 3]) for i in range(len(ref_ids)) if mine[i] != ref_ids[i])
 
 

@@ -78,6 +78,41 @@ def test_unigram_matches_sentencepiece(tmp_path):
     assert tok.encode("the ZZ dog") == sp.encode("the ZZ dog") + [sp.eos_id()]
 
 
+def test_unigram_with_precompiled_charsmap_matches_sentencepiece(tmp_path):
+    """The model's own normalisation table (nmt_nfkc, 240 kB double-array trie) read from the file: ligatures, full-width forms, circled digits,
+    square katakana words, half-width katakana with voicing marks, zero-width and ideographic spaces - normalised and tokenised as sentencepiece
+    does."""
+    spm = pytest.importorskip("sentencepiece")
+    from sentencepiece import sentencepiece_model_pb2 as pb
+    corpus = tmp_path / "corpus.txt"
+    base = ["the quick brown fox jumps over the lazy dog", "hello world this is a test", "fine ABC abc 123 VIII", "price is five dollars approximately"]
+    corpus.write_text("\n".join(base * 40) + "\n")
+    prefix = str(tmp_path / "ugm")
+    spm.SentencePieceTrainer.train(input=str(corpus), model_prefix=prefix, vocab_size=110, model_type="unigram", character_coverage=1.0,
+                                   bos_id=-1, eos_id=1, unk_id=2, pad_id=0, hard_vocab_limit=False, minloglevel=2, user_defined_symbols=["<ｘ>"])
+    sp = spm.SentencePieceProcessor(model_file=prefix + ".model")
+    proto = pb.ModelProto()
+    proto.ParseFromString(open(prefix + ".model", "rb").read())
+    charsmap = proto.normalizer_spec.precompiled_charsmap
+    assert proto.normalizer_spec.name == "nmt_nfkc" and len(charsmap) > 100000
+    n = sp.get_piece_size()
+    types = [int(TokenType.CONTROL) if sp.is_control(i) else int(TokenType.UNKNOWN) if sp.is_unknown(i) else
+             int(TokenType.USER_DEFINED) if proto.pieces[i].type == 4 else int(TokenType.NORMAL) for i in range(n)]
+    meta = {"tokenizer.ggml.model": "t5", "tokenizer.ggml.tokens": [sp.id_to_piece(i) for i in range(n)], "tokenizer.ggml.scores": [sp.get_score(i) for i in range(n)],
+            "tokenizer.ggml.token_type": types, "tokenizer.ggml.unknown_token_id": sp.unk_id(), "tokenizer.ggml.eos_token_id": sp.eos_id(),
+            "tokenizer.ggml.add_eos_token": False, "tokenizer.ggml.add_bos_token": False, "tokenizer.ggml.precompiled_charsmap": list(charsmap)}
+    tok = Tokenizer(meta)
+    assert tok.codec.charsmap is not None
+    for s in ["ﬁne ＡＢＣ ① test", "ｈｅｌｌｏ\u3000ｗｏｒｌｄ", "the\u200bquick  brown", "Ⅷ dollars", "ｶﾞ ㌔ fox", "tab\there", "plain text"]:
+        assert tok.codec.normalize(s) == sp.normalize(s), s
+        assert tok.encode(s) == sp.encode(s), s
+    # a user-defined symbol is protected from the table (its full-width letter stays); around it the text is cut into fragments first, as the
+    # reference does (`tokenizer_st_partition`), so the spaces next to it are trimmed where sentencepiece itself keeps one
+    assert tok.codec.normalize("a <ｘ> b ＡＢＣ") == sp.normalize("a <ｘ> b ＡＢＣ")
+    ids = tok.encode("a <ｘ> b ＡＢＣ")
+    assert sp.piece_to_id("<ｘ>") in ids and tok.decode(ids).replace(" ", "") == "a<ｘ>bABC"
+
+
 def test_rwkv_trie_and_escapes():
     assert unescape_rwkv("\\n") == b"\n" and unescape_rwkv("\\x0a\\xe4") == b"\n\xe4" and unescape_rwkv("a\\\\b") == b"a\\b" and unescape_rwkv("é") == "é".encode()
     toks = ["<s>"] + [f"\\x{b:02x}" for b in range(256)] + ["he", "hello", "hell", " wor", "ld", "\\xe6\\x97\\xa5"]
