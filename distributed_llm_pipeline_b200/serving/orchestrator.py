@@ -654,41 +654,63 @@ class ModelRouter(Orchestrator):
 
     Parity: llama-server's router mode (`tools/server/server-models.cpp:415-600`: spawn / monitor child servers, LRU unload)
     and `--sleep-idle-seconds` (`server-context.cpp:651-665`); here the models share the process instead of being child
-    processes (the native front-end `runtime/orchestrator.cpp` supervises the process as a whole)."""
+    processes (the native front-end `runtime/orchestrator.cpp` supervises the process as a whole).
+
+    `replicas` > 1 loads every model that many times (data parallelism: replica i on `cuda:(i mod device count)` when the device is
+    "cuda", each with its own scheduler, slots and KV cache) and sends each request to the replica with the fewest requests in flight."""
 
     def __init__(self, models: dict[str, str], build_kw: dict | None = None, max_loaded: int = 1, sleep_idle_s: float = 0.0,
-                 static_dir: str = STATIC_DIR, n_predict: int = 200, **orch_kw):
+                 static_dir: str = STATIC_DIR, n_predict: int = 200, replicas: int = 1, **orch_kw):
         super().__init__(None, {"name": "router"}, static_dir, n_predict, api_key=orch_kw.get("api_key"))
         self.models = dict(models)
         self.build_kw = build_kw or {}
         self.max_loaded = max(1, max_loaded)
         self.sleep_idle_s = sleep_idle_s
         self.orch_kw = orch_kw
-        self.loaded: dict[str, Orchestrator] = {}
+        self.replicas = max(1, int(replicas))
+        self.loaded: dict[str, list[Orchestrator]] = {}      # model name -> its replicas
         self.last_used: dict[str, float] = {}
         self.n_loads = 0
+        self._rr = 0
         self._load_lock = asyncio.Lock()
 
     @staticmethod
-    def _busy(o: Orchestrator) -> bool:
-        return bool(o.sched.queue) or any(s.state.name != "IDLE" for s in o.sched.slots)
+    def _in_flight(o: Orchestrator) -> int:
+        return len(o.sched.queue) + sum(s.state.name != "IDLE" for s in o.sched.slots)
+
+    @classmethod
+    def _busy(cls, group: list[Orchestrator]) -> bool:
+        return any(cls._in_flight(o) for o in group)
+
+    def _pick(self, group: list[Orchestrator]) -> Orchestrator:
+        """Least requests in flight; ties go round so that an idle group is used evenly."""
+        self._rr += 1
+        return min(enumerate(group), key=lambda io: (self._in_flight(io[1]), (io[0] - self._rr) % len(group)))[1]
 
     def _unload(self, name: str):
-        o = self.loaded.pop(name, None)
-        if o is not None:
-            o.sched.stop()
-            del o
+        group = self.loaded.pop(name, None)
+        if group is not None:
+            for o in group:
+                o.sched.stop()
+            del group
             import gc
             import torch
             gc.collect()
             if torch.cuda.is_available():
                 torch.cuda.empty_cache()
 
-    def _load(self, name: str) -> Orchestrator:
-        sched, info, logs = build_service(self.models[name], **self.build_kw)
-        sched.start()
+    def _load(self, name: str) -> list[Orchestrator]:
+        import torch
+        group = []
+        for i in range(self.replicas):
+            kw = dict(self.build_kw)
+            if self.replicas > 1 and str(kw.get("device", "cuda")) == "cuda" and torch.cuda.is_available():
+                kw["device"] = f"cuda:{i % torch.cuda.device_count()}"
+            sched, info, logs = build_service(self.models[name], **kw)
+            sched.start()
+            group.append(Orchestrator(sched, info, self.static_dir, self.n_predict, logs, **self.orch_kw))
         self.n_loads += 1
-        return Orchestrator(sched, info, self.static_dir, self.n_predict, logs, **self.orch_kw)
+        return group
 
     async def acquire(self, name: str) -> Orchestrator:
         async with self._load_lock:
@@ -701,7 +723,7 @@ class ModelRouter(Orchestrator):
                     self._unload(idle[0])
                 self.loaded[name] = await asyncio.get_running_loop().run_in_executor(None, self._load, name)
             self.last_used[name] = time.time()
-            return self.loaded[name]
+            return self._pick(self.loaded[name])
 
     async def reap_idle(self):
         """Background task: unload models nobody has used for sleep_idle_s seconds."""
@@ -719,7 +741,8 @@ class ModelRouter(Orchestrator):
                  "status": "loaded" if n in self.loaded else "unloaded"} for n, p in self.models.items()]})
             return True
         if method == "GET" and path == "/health":
-            await self._json(writer, {"status": "ok", "models_loaded": sorted(self.loaded), "loads": self.n_loads})
+            await self._json(writer, {"status": "ok", "models_loaded": sorted(self.loaded), "loads": self.n_loads, "replicas": self.replicas,
+                                      "in_flight": {n: [self._in_flight(o) for o in g] for n, g in self.loaded.items()}})
             return True
         if method in ("GET", "HEAD", "OPTIONS") and path not in ("/metrics", "/slots", "/props"):
             return await super().route(method, path, headers, body, reader, writer)
@@ -891,6 +914,7 @@ def main(argv=None):
     ap.add_argument("-m", "--model", default=None)
     ap.add_argument("--models", default=None, help="router mode: comma separated name=path.gguf list (or a directory of .gguf files)")
     ap.add_argument("--models-max", type=int, default=1, help="router mode: models kept resident at once")
+    ap.add_argument("--replicas", type=int, default=1, help="router mode: copies of each model (one per GPU in turn); requests go to the least busy copy")
     ap.add_argument("--sleep-idle-seconds", type=float, default=0.0, help="router mode: unload a model after this many idle seconds")
     ap.add_argument("--host", default=os.environ.get("DLP_HOST", "0.0.0.0"))
     ap.add_argument("--port", type=int, default=int(os.environ.get("DLP_PORT", "3005")))
@@ -915,7 +939,7 @@ def main(argv=None):
         else:
             models = dict(item.split("=", 1) if "=" in item else (os.path.splitext(os.path.basename(item))[0], item) for item in a.models.split(","))
         router = ModelRouter(models, dict(device=a.device, n_ctx=a.ctx_size, n_slots=a.parallel, n_batch=a.batch_size), a.models_max,
-                             a.sleep_idle_seconds, a.static, a.predict, api_key=a.api_key, max_queue=a.max_queue, slot_save_path=a.slot_save_path)
+                             a.sleep_idle_seconds, a.static, a.predict, replicas=a.replicas, api_key=a.api_key, max_queue=a.max_queue, slot_save_path=a.slot_save_path)
         print(f"dlp_b200 router ready: http://localhost:{a.port} ({len(models)} models)", flush=True)
         try:
             asyncio.run(router.serve(a.host, a.port))

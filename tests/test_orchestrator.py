@@ -285,6 +285,24 @@ def test_model_router_loads_on_demand_and_unloads_lru(tmp_models):
     assert json.loads(body)["models_loaded"] == []
 
 
+def test_model_router_spreads_requests_over_replicas(tmp_models):
+    """`--replicas 2`: two copies of the model, each with one slot; six concurrent requests are split between them by the number of requests in
+    flight, both copies serve some, and every answer is the same deterministic text."""
+    import concurrent.futures
+    from distributed_llm_pipeline_b200.serving.orchestrator import ModelRouter
+    router = ModelRouter({"m": tmp_models[("tiny", "F16")]}, dict(device="cpu", n_ctx=64, n_slots=1, n_batch=32), max_loaded=1, n_predict=4, replicas=2)
+    port = _serve(router)
+    req = json.dumps({"model": "m", "prompt": "a b c d e", "n_predict": 12, "temperature": 0, "cache_prompt": False}).encode()
+    first = json.loads(_http(port, "POST", "/completion", req)[2])["content"]          # loads the group
+    with concurrent.futures.ThreadPoolExecutor(6) as ex:
+        outs = list(ex.map(lambda _: json.loads(_http(port, "POST", "/completion", req)[2])["content"], range(6)))
+    assert outs == [first] * 6
+    h = json.loads(_http(port, "GET", "/health")[2])
+    assert h["replicas"] == 2 and h["loads"] == 1 and h["in_flight"] == {"m": [0, 0]}
+    served = [o.sched.metrics.c["requests_total"] for o in router.loaded["m"]]
+    assert sum(served) == 7 and min(served) >= 2, served
+
+
 def test_ollama_and_anthropic_dialects(server):
     port, _ = server
     _, _, body = _http(port, "POST", "/api/generate", json.dumps({"prompt": "a b c", "stream": False, "options": {"num_predict": 4, "temperature": 0}}).encode())
