@@ -16,7 +16,8 @@
 
 namespace dlp_gguf {
 
-enum GType : uint32_t { T_F32 = 0, T_F16 = 1, T_Q8_0 = 8, T_Q4_K = 12, T_Q5_K = 13, T_Q6_K = 14, T_BF16 = 30 };
+enum GType : uint32_t { T_F32 = 0, T_F16 = 1, T_Q4_0 = 2, T_Q4_1 = 3, T_Q5_0 = 6, T_Q5_1 = 7, T_Q8_0 = 8, T_Q2_K = 10, T_Q3_K = 11, T_Q4_K = 12, T_Q5_K = 13,
+                        T_Q6_K = 14, T_IQ4_NL = 20, T_IQ4_XS = 23, T_BF16 = 30 };
 
 // ---- GGUF -----------------------------------------------------------------------------------------------------------
 struct Tensor {
@@ -42,6 +43,13 @@ inline size_t row_bytes(uint32_t type, uint64_t k) {
         case T_F32: return k * 4;
         case T_F16: case T_BF16: return k * 2;
         case T_Q8_0: return k / 32 * 34;
+        case T_Q4_0: case T_IQ4_NL: return k / 32 * 18;
+        case T_Q4_1: return k / 32 * 20;
+        case T_Q5_0: return k / 32 * 22;
+        case T_Q5_1: return k / 32 * 24;
+        case T_Q2_K: return k / 256 * 84;
+        case T_Q3_K: return k / 256 * 110;
+        case T_IQ4_XS: return k / 256 * 136;
         case T_Q4_K: return k / 256 * 144;
         case T_Q5_K: return k / 256 * 176;
         case T_Q6_K: return k / 256 * 210;
@@ -195,6 +203,87 @@ inline void decode_row(uint32_t type, const uint8_t* src, uint64_t k, float* out
                     }
                     y += 128; ql += 64; qh += 32; sc += 8;
                 }
+            }
+            break;
+        // legacy 4- and 5-bit blocks of 32: fp16 scale (and minimum for the _1 kinds), the fifth bits of Q5 in one little-endian word,
+        // nibbles with element j in the low half of byte j and element j + 16 in the high half
+        case T_Q4_0: case T_Q4_1: case T_Q5_0: case T_Q5_1: case T_IQ4_NL: {
+            static const float iq4[16] = {-127, -104, -83, -65, -49, -35, -22, -10, 1, 13, 25, 38, 53, 69, 89, 113};
+            const bool has_min = type == T_Q4_1 || type == T_Q5_1, five = type == T_Q5_0 || type == T_Q5_1;
+            const size_t bs = row_bytes(type, 32);
+            for (uint64_t b = 0; b < k / 32; ++b) {
+                const uint8_t* p = src + b * bs;
+                uint16_t dh, mh = 0; memcpy(&dh, p, 2); p += 2;
+                if (has_min) { memcpy(&mh, p, 2); p += 2; }
+                uint32_t hb = 0;
+                if (five) { memcpy(&hb, p, 4); p += 4; }
+                const float d = f16(dh), m = has_min ? f16(mh) : 0.0f;
+                float* y = out + b * 32;
+                for (int i = 0; i < 16; ++i) {
+                    int lo = p[i] & 0xF, hi = p[i] >> 4;
+                    if (five) { lo |= ((hb >> i) & 1) << 4; hi |= ((hb >> (i + 16)) & 1) << 4; }
+                    if (type == T_IQ4_NL) { y[i] = d * iq4[lo]; y[i + 16] = d * iq4[hi]; }
+                    else if (has_min) { y[i] = d * lo + m; y[i + 16] = d * hi + m; }
+                    else { const int off = five ? 16 : 8; y[i] = d * (lo - off); y[i + 16] = d * (hi - off); }
+                }
+            }
+            break;
+        }
+        case T_IQ4_XS:      // 256 values: fp16 scale, eight 6-bit sub-block scales (two high bits in one word, low nibbles in 4 bytes), non-linear nibbles
+            for (uint64_t b = 0; b < k / 256; ++b) {
+                static const float iq4[16] = {-127, -104, -83, -65, -49, -35, -22, -10, 1, 13, 25, 38, 53, 69, 89, 113};
+                const uint8_t* p = src + b * 136;
+                uint16_t dh, sh; memcpy(&dh, p, 2); memcpy(&sh, p + 2, 2);
+                const float d = f16(dh);
+                const uint8_t* sl = p + 4; const uint8_t* q = p + 8;
+                float* y = out + b * 256;
+                for (int ib = 0; ib < 8; ++ib) {
+                    const int ls = (((sl[ib / 2] >> (4 * (ib % 2))) & 0xF) | (((sh >> (2 * ib)) & 3) << 4)) - 32;
+                    const float dl = d * ls;
+                    for (int i = 0; i < 16; ++i) { y[i] = dl * iq4[q[i] & 0xF]; y[i + 16] = dl * iq4[q[i] >> 4]; }
+                    y += 32; q += 16;
+                }
+            }
+            break;
+        case T_Q2_K:        // 16 sub-blocks of 16: 4-bit scale | 4-bit minimum per sub-block, 2-bit values in four bit planes per 32 bytes
+            for (uint64_t b = 0; b < k / 256; ++b) {
+                const uint8_t* p = src + b * 84;
+                const uint8_t* sc = p; const uint8_t* q = p + 16;
+                uint16_t dh, mh; memcpy(&dh, p + 80, 2); memcpy(&mh, p + 82, 2);
+                const float d = f16(dh), dm = f16(mh);
+                float* y = out + b * 256;
+                int is = 0;
+                for (int half = 0; half < 2; ++half, q += 32)
+                    for (int sh = 0; sh < 8; sh += 2)
+                        for (int part = 0; part < 2; ++part, ++is) {
+                            const float dl = d * (sc[is] & 0xF), ml = dm * (sc[is] >> 4);
+                            for (int l = 0; l < 16; ++l) *y++ = dl * ((q[part * 16 + l] >> sh) & 3) - ml;
+                        }
+            }
+            break;
+        case T_Q3_K:        // low 2 bits in bit planes, the third bit in hmask (set = no -4 offset), sixteen 6-bit scales packed in 12 bytes
+            for (uint64_t b = 0; b < k / 256; ++b) {
+                const uint8_t* p = src + b * 110;
+                const uint8_t* hm = p; const uint8_t* q = p + 32; const uint8_t* s12 = p + 96;
+                uint16_t dh; memcpy(&dh, p + 108, 2);
+                const float d = f16(dh);
+                int scales[16];
+                for (int j = 0; j < 16; ++j) {
+                    const int lo = j < 8 ? (s12[j] & 0xF) : (s12[j - 8] >> 4);
+                    const int hi = (s12[8 + j % 4] >> (2 * (j / 4))) & 3;
+                    scales[j] = (lo | (hi << 4)) - 32;
+                }
+                float* y = out + b * 256;
+                int is = 0, bit = 0;
+                for (int half = 0; half < 2; ++half, q += 32)
+                    for (int sh = 0; sh < 8; sh += 2, ++bit)
+                        for (int part = 0; part < 2; ++part, ++is) {
+                            const float dl = d * scales[is];
+                            for (int l = 0; l < 16; ++l) {
+                                const int idx = part * 16 + l;
+                                *y++ = dl * ((int)((q[idx] >> sh) & 3) - (((hm[idx] >> bit) & 1) ? 0 : 4));
+                            }
+                        }
             }
             break;
         default: throw std::runtime_error("decode_row: unsupported type");

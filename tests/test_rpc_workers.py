@@ -182,3 +182,28 @@ def test_worker_bench_mode(tmp_models):
                        capture_output=True, text=True, timeout=120)
     assert p.returncode == 0, p.stderr
     assert "bench: prefill 16 tokens" in p.stderr and "matmul" in p.stderr
+
+
+@pytest.mark.parametrize("ftype", ["Q4_0", "Q4_1", "Q5_0", "Q5_1", "Q2_K", "Q3_K", "IQ4_NL", "IQ4_XS"])
+def test_cpu_workers_read_the_other_block_types(tmp_path, ftype):
+    """The legacy 4- / 5-bit blocks, the 2- and 3-bit K-quants and the non-linear 4-bit kinds through two native stage workers: the row decoders
+    of `runtime/gguf_lite.h` against the numpy codecs behind the oracle (prefill and one decode step)."""
+    from distributed_llm_pipeline_b200.gguf import write_synthetic_gguf
+    from distributed_llm_pipeline_b200.models.config import preset
+    path = write_synthetic_gguf(str(tmp_path / f"tiny-{ftype}.gguf"), preset("tiny"), ftype, seed=1)
+    procs, eps = launch_local_workers(path, 2, base_port=_free_base(2), n_ctx=64, threads=2)
+    eng = None
+    try:
+        eng = RpcEngine(eps, max_seqs=1)
+        ref = ReferenceModel.from_gguf(path)
+        prompt = [1, 5, 9, 200, 33, 7, 8, 100, 42]
+        sid = eng.alloc_seq()
+        got = torch.as_tensor(eng.prefill(sid, prompt)).float()
+        assert nmse(got, ref.forward(torch.tensor(prompt), ref.new_cache(64))[-1]) < 1e-9
+        step = torch.as_tensor(eng.decode([sid], [7], sample=False)[0]).float()
+        assert nmse(step, ref.forward(torch.tensor(prompt + [7]), ref.new_cache(64))[-1]) < 1e-9
+    finally:
+        for w in (eng.workers if eng is not None else []):
+            w.shutdown()
+        for p in procs:
+            p.wait(timeout=10)
