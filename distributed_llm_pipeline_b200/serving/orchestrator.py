@@ -75,6 +75,42 @@ def apply_chat_template(meta: dict, messages: list[dict]) -> str:
     return chat_templates.apply("chatml", messages)
 
 
+FINGERPRINT = "dlp_b200"
+
+
+def _as(kind, value, default):
+    """`value` as `kind`, or `default` when it is absent or of the wrong type (llama-server's json_value falls back the same way)."""
+    if value is None or isinstance(value, bool) and kind is not bool:
+        return default
+    try:
+        return kind(value)
+    except (TypeError, ValueError):
+        return default
+
+
+def _logit_bias(v) -> dict[int, float]:
+    """`logit_bias` as {token id: bias} from either wire form ({"id": bias} or [[id, bias], ...]); `false` as a bias means "never" (-inf);
+    entries that are not numbers are skipped."""
+    pairs = v.items() if isinstance(v, dict) else [x for x in (v or []) if isinstance(x, (list, tuple)) and len(x) == 2] if isinstance(v, list) else []
+    out = {}
+    for k_, b in pairs:
+        try:
+            out[int(k_)] = float("-inf") if b is False else float(b)
+        except (TypeError, ValueError):
+            continue
+    return out
+
+
+def _logprob_items(items: list[dict]) -> list[dict]:
+    """OpenAI `logprobs.content` entries from the scheduler's per-token records (post-sampling records carry probabilities: take their logs)."""
+    import math
+
+    def one(p):
+        lp = p["logprob"] if "logprob" in p else (math.log(p["prob"]) if p.get("prob", 0) > 0 else -9999.0)
+        return {"id": p["id"], "token": p["token"], "bytes": p.get("bytes", []), "logprob": lp}
+    return [{**one(p), "top_logprobs": [one(t) for t in p.get("top_logprobs", p.get("top_probs", []))]} for p in items]
+
+
 class Orchestrator:
     def __init__(self, scheduler: Scheduler, model_info: dict | None = None, static_dir: str = STATIC_DIR, n_predict: int = 200,
                  startup_logs: list[str] | None = None, api_key: str | None = None, max_queue: int = 0,
@@ -196,7 +232,18 @@ class Orchestrator:
                 return await self.anthropic_messages(json.loads(body or b"{}"), writer)
             if method == "POST" and path == "/tokenize":
                 d = json.loads(body or b"{}")
-                await self._json(writer, {"tokens": self.sched.tok.encode(d.get("content", ""), add_bos=bool(d.get("add_special", False)))})
+                t = self.sched.tok
+                ids = t.encode(d.get("content", ""), add_bos=bool(d.get("add_special", False)))
+                if d.get("with_pieces"):      # a piece that is not valid UTF-8 on its own is given as its bytes
+                    def piece(i):
+                        b = t.token_bytes(i) if t.types[i] != 3 else t.tokens[i].encode("utf-8")
+                        try:
+                            return b.decode("utf-8")
+                        except UnicodeDecodeError:
+                            return list(b)
+                    await self._json(writer, {"tokens": [{"id": i, "piece": piece(i)} for i in ids]})
+                else:
+                    await self._json(writer, {"tokens": ids})
                 return True
             if method == "POST" and path == "/detokenize":
                 await self._json(writer, {"content": self.sched.tok.decode(json.loads(body or b"{}").get("tokens", []), False)})
@@ -256,7 +303,12 @@ class Orchestrator:
             await self._json(writer, {"error": "not found"}, "404 Not Found")
             return True
         except json.JSONDecodeError as e:
-            await self._json(writer, {"error": f"invalid JSON: {e}"}, "400 Bad Request")
+            await self._json(writer, *self._bad_request(f"invalid JSON: {e}"))
+            return True
+        except (ConnectionError, asyncio.CancelledError):
+            raise
+        except (KeyError, TypeError, ValueError, AttributeError) as e:      # a well-formed body of the wrong shape: answer, never drop the connection
+            await self._json(writer, *self._bad_request(f"{type(e).__name__}: {e}"))
             return True
 
     async def slot_action(self, path: str, d: dict, writer) -> bool:
@@ -382,7 +434,7 @@ class Orchestrator:
     # ---- llama-server style / OpenAI style completions -----------------------------------------------------------
     def _sampling_from(self, d: dict) -> SamplingParams:
         schema = d.get("json_schema")
-        rf = d.get("response_format") or {}
+        rf = d.get("response_format") if isinstance(d.get("response_format"), dict) else {}
         if schema is None and rf.get("type") == "json_object":
             schema = rf.get("schema") or {}
         if schema is None and rf.get("type") == "json_schema":
@@ -393,73 +445,132 @@ class Orchestrator:
         return SamplingParams(grammar=str(d.get("grammar", "") or ""), json_schema=schema,
                               grammar_lazy=bool(d.get("grammar_lazy", False)), grammar_trigger_words=words, grammar_trigger_patterns=pats,
                               infill=bool(d.get("infill_sampler", False)) or "infill" in (d.get("samplers") or []),
-                              top_n_sigma=float(d.get("top_n_sigma", -1.0)), dynatemp_range=float(d.get("dynatemp_range", 0.0)),
-                              dynatemp_exponent=float(d.get("dynatemp_exponent", 1.0)), xtc_probability=float(d.get("xtc_probability", 0.0)),
-                              xtc_threshold=float(d.get("xtc_threshold", 0.1)), mirostat=int(d.get("mirostat", 0)),
-                              mirostat_tau=float(d.get("mirostat_tau", 5.0)), mirostat_eta=float(d.get("mirostat_eta", 0.1)),
-                              dry_multiplier=float(d.get("dry_multiplier", 0.0)), dry_base=float(d.get("dry_base", 1.75)),
-                              dry_allowed_length=int(d.get("dry_allowed_length", 2)), dry_penalty_last_n=int(d.get("dry_penalty_last_n", -1)),
+                              top_n_sigma=_as(float, d.get("top_n_sigma"), -1.0), dynatemp_range=_as(float, d.get("dynatemp_range"), 0.0),
+                              dynatemp_exponent=_as(float, d.get("dynatemp_exponent"), 1.0), xtc_probability=_as(float, d.get("xtc_probability"), 0.0),
+                              xtc_threshold=_as(float, d.get("xtc_threshold"), 0.1), mirostat=_as(int, d.get("mirostat"), 0),
+                              mirostat_tau=_as(float, d.get("mirostat_tau"), 5.0), mirostat_eta=_as(float, d.get("mirostat_eta"), 0.1),
+                              dry_multiplier=_as(float, d.get("dry_multiplier"), 0.0), dry_base=_as(float, d.get("dry_base"), 1.75),
+                              dry_allowed_length=_as(int, d.get("dry_allowed_length"), 2), dry_penalty_last_n=_as(int, d.get("dry_penalty_last_n"), -1),
                               dry_breakers=tuple(t for b in (d.get("dry_sequence_breakers") if d.get("dry_sequence_breakers") is not None else ["\n", ":", "\"", "*"])
                                                  for t in self.sched.tok.encode(str(b), add_bos=False)[-1:]),
-                              repeat_last_n=int(d.get("repeat_last_n", 64)),
-                              logit_bias={int(k): float(v) for k, v in (d.get("logit_bias") or {}).items()} if isinstance(d.get("logit_bias"), dict)
-                              else {int(k): float(v) for k, v in (d.get("logit_bias") or [])},
-                              temperature=float(d.get("temperature", 0.8)), top_k=int(d.get("top_k", 40)), top_p=float(d.get("top_p", 0.95)),
-                              min_p=float(d.get("min_p", 0.05)), typical_p=float(d.get("typical_p", 1.0)),
-                              repeat_penalty=float(d.get("repeat_penalty", 1.0)), frequency_penalty=float(d.get("frequency_penalty", 0.0)),
-                              presence_penalty=float(d.get("presence_penalty", 0.0)), seed=int(d.get("seed", 0) if d.get("seed", 0) >= 0 else 0))
+                              repeat_last_n=_as(int, d.get("repeat_last_n"), 64),
+                              logit_bias=_logit_bias(d.get("logit_bias")),
+                              temperature=_as(float, d.get("temperature"), 0.8), top_k=_as(int, d.get("top_k"), 40), top_p=_as(float, d.get("top_p"), 0.95),
+                              min_p=_as(float, d.get("min_p"), 0.05), typical_p=_as(float, d.get("typical_p"), 1.0),
+                              repeat_penalty=_as(float, d.get("repeat_penalty"), 1.0), frequency_penalty=_as(float, d.get("frequency_penalty"), 0.0),
+                              presence_penalty=_as(float, d.get("presence_penalty"), 0.0), seed=max(0, _as(int, d.get("seed"), 0)))
 
-    async def completion(self, d: dict, writer, openai=False) -> bool:
+    def _bad_request(self, message: str) -> tuple[dict, str]:
+        return {"error": {"code": 400, "message": message, "type": "invalid_request_error"}}, "400 Bad Request"
+
+    def _request_from(self, d: dict, prompt, openai: bool) -> Request:
         stop = d.get("stop") or []
-        stop = [stop] if isinstance(stop, str) else list(stop)
-        n_predict = int(d.get("n_predict", d.get("max_tokens", self.n_predict)))
-        req = Request(prompt=d.get("prompt", ""), n_predict=n_predict if n_predict > 0 else self.sched.eng.n_ctx,
-                      sampling=self._sampling_from(d), stop=stop, cache_prompt=bool(d.get("cache_prompt", True)),
-                      ignore_eos=bool(d.get("ignore_eos", False)), n_keep=int(d.get("n_keep", 0)),
-                      n_draft=int(d.get("speculative.n_max", d.get("n_draft", 0)) or 0),
-                      n_probs=int(d.get("n_probs", 0) or 0) or (int(d.get("logprobs") or 0) if openai else 0))
+        stop = [stop] if isinstance(stop, str) else [str(x) for x in stop]
+        try:
+            n_predict = int(d.get("n_predict", d.get("max_tokens", self.n_predict)))
+        except (TypeError, ValueError):
+            n_predict = self.n_predict
+        # -1 = until EOS or a full context; any other value below 1 still yields the token sampled from the prompt (the reference checks
+        # its budget only after a token has been produced, server-context.cpp process_token)
+        limit = self.sched.eng.n_ctx if n_predict == -1 else max(1, n_predict)
+        req = Request(prompt=prompt, n_predict=limit, sampling=self._sampling_from(d), stop=stop, cache_prompt=bool(d.get("cache_prompt", True)),
+                      ignore_eos=bool(d.get("ignore_eos", False)), n_keep=_as(int, d.get("n_keep"), 0),
+                      n_draft=_as(int, d.get("speculative.n_max", d.get("n_draft")), 0),
+                      n_probs=_as(int, d.get("n_probs"), 0) or (_as(int, d.get("logprobs"), 0) if openai else 0),
+                      post_sampling_probs=bool(d.get("post_sampling_probs", False)))
+        req.n_predict_asked = n_predict
+        return req
+
+    def _generation_settings(self, req: Request, d: dict) -> dict:
+        """What the request ran with, under llama-server's names (`server_task_result_cmpl_final::to_json`, server-task.cpp)."""
+        sp = req.sampling
+        return {"seed": sp.seed, "temperature": sp.temperature, "dynatemp_range": sp.dynatemp_range, "dynatemp_exponent": sp.dynatemp_exponent,
+                "top_k": sp.top_k, "top_p": sp.top_p, "min_p": sp.min_p, "top_n_sigma": sp.top_n_sigma, "xtc_probability": sp.xtc_probability,
+                "xtc_threshold": sp.xtc_threshold, "typical_p": sp.typical_p, "repeat_last_n": sp.repeat_last_n, "repeat_penalty": sp.repeat_penalty,
+                "presence_penalty": sp.presence_penalty, "frequency_penalty": sp.frequency_penalty, "dry_multiplier": sp.dry_multiplier,
+                "dry_base": sp.dry_base, "dry_allowed_length": sp.dry_allowed_length, "dry_penalty_last_n": sp.dry_penalty_last_n,
+                "dry_sequence_breakers": d.get("dry_sequence_breakers") if d.get("dry_sequence_breakers") is not None else ["\n", ":", "\"", "*"],
+                "mirostat": sp.mirostat, "mirostat_tau": sp.mirostat_tau, "mirostat_eta": sp.mirostat_eta, "stop": list(req.stop),
+                "max_tokens": getattr(req, "n_predict_asked", req.n_predict), "n_predict": getattr(req, "n_predict_asked", req.n_predict),
+                "n_keep": req.n_keep, "n_discard": 0, "ignore_eos": req.ignore_eos, "stream": bool(d.get("stream", False)),
+                "logit_bias": [[k, v] for k, v in sp.logit_bias.items()], "n_probs": req.n_probs, "min_keep": 0, "grammar": sp.grammar,
+                "grammar_lazy": sp.grammar_lazy, "grammar_triggers": list(d.get("grammar_triggers") or []), "preserved_tokens": [],
+                "chat_format": "Content-only", "reasoning_format": "none", "reasoning_in_content": False, "thinking_forced_open": False,
+                "samplers": ["penalties", "dry", "top_n_sigma", "top_k", "typ_p", "top_p", "min_p", "xtc", "temperature"],
+                "speculative.n_max": req.n_draft or getattr(self.sched, "n_draft_default", 0), "speculative.n_min": 0, "speculative.p_min": 0.0,
+                "timings_per_token": bool(d.get("timings_per_token", False)), "post_sampling_probs": req.post_sampling_probs,
+                "backend_sampling": False, "lora": []}
+
+    def _native_final(self, req: Request, d: dict, index: int = 0, content: str | None = None) -> dict:
+        """The closing record of `/completion` (also the last stream event): every field of the reference's, in its order."""
+        return {"index": index, "content": req.text if content is None else content,
+                "tokens": list(req.output_ids) if (d.get("return_tokens") and content is None) else [], "id_slot": req.id_slot, "stop": True,
+                "model": self.info.get("name", "model"), "tokens_predicted": len(req.output_ids), "tokens_evaluated": len(req.prompt_ids),
+                "generation_settings": self._generation_settings(req, d), "prompt": self.sched.tok.decode_with_specials(req.prompt_ids),
+                "has_new_line": "\n" in req.text, "truncated": req.truncated, "stop_type": req.stop_type, "stopping_word": req.stopping_word,
+                "tokens_cached": req.tokens_cached, "timings": req.timings(),
+                **({"completion_probabilities": req.probs} if req.n_probs > 0 and content is None else {})}
+
+    def _openai_text(self, req: Request, rid: str) -> dict:
+        return {"choices": [{"text": req.text, "index": 0, "logprobs": {"content": _logprob_items(req.probs)} if req.n_probs > 0 else None,
+                             "finish_reason": req.finish_reason}],
+                "created": int(time.time()), "model": self.info.get("name", "model"), "system_fingerprint": FINGERPRINT, "object": "text_completion",
+                "usage": {"completion_tokens": len(req.output_ids), "prompt_tokens": len(req.prompt_ids),
+                          "total_tokens": len(req.prompt_ids) + len(req.output_ids)}, "id": rid, "timings": req.timings()}
+
+    async def completion(self, d, writer, openai=False) -> bool:
+        if not isinstance(d, dict):
+            await self._json(writer, *self._bad_request("the request body must be a JSON object"))
+            return True
+        if "prompt" not in d:
+            await self._json(writer, *self._bad_request("key 'prompt' not found"))
+            return True
+        prompt = d["prompt"]
+        # an array of prompts (strings or token arrays; a flat array of integers is ONE prompt) runs as one request each and answers with an array
+        many = isinstance(prompt, list) and any(not isinstance(x, int) for x in prompt) and not d.get("stream")
+        if many:
+            reqs = [self._request_from(d, x, openai) for x in prompt]
+            await asyncio.gather(*(self._run_blocking(r) for r in reqs))
+            if openai:
+                out = self._openai_text(reqs[0], "cmpl-" + uuid.uuid4().hex[:24])
+                out["choices"] = [{**self._openai_text(r, "")["choices"][0], "index": k} for k, r in enumerate(reqs)]
+                await self._json(writer, out)
+            else:
+                await self._json(writer, [self._native_final(r, d, k) for k, r in enumerate(reqs)])
+            return True
+        req = self._request_from(d, prompt, openai)
         rid = "cmpl-" + uuid.uuid4().hex[:24]
-
-        def native_probs(items):      # llama-server `completion_probabilities` (server-task.cpp): one entry per generated token
-            return [{"id": p["id"], "token": p["token"], "logprob": p["logprob"], "top_logprobs": p["top_logprobs"]} for p in items]
-
-        def openai_logprobs(items):   # legacy /v1/completions `logprobs` object
-            return {"tokens": [p["token"] for p in items], "token_logprobs": [p["logprob"] for p in items],
-                    "top_logprobs": [{t["token"]: t["logprob"] for t in p["top_logprobs"]} for p in items]}
-        sent = [0]
+        sent, sent_tok = [0], [0]
         if d.get("stream"):
             writer.write(self._head("200 OK", [("content-type", "text/event-stream"), ("cache-control", "no-cache")] + CORS + [("connection", "close")]))
 
             def fmt(kind, content):
                 if kind == "token":
-                    obj = ({"id": rid, "object": "text_completion", "choices": [{"index": 0, "text": content, "finish_reason": None}]}
-                           if openai else {"content": content, "stop": False})
+                    ids, sent_tok[0] = req.output_ids[sent_tok[0]:], len(req.output_ids)
+                    obj = ({"id": rid, "object": "text_completion", "created": int(time.time()), "model": self.info.get("name", "model"),
+                            "system_fingerprint": FINGERPRINT, "choices": [{"index": 0, "text": content, "logprobs": None, "finish_reason": None}]}
+                           if openai else {"index": 0, "content": content, "tokens": list(ids), "stop": False, "id_slot": -1,
+                                           "tokens_predicted": len(req.output_ids), "tokens_evaluated": len(req.prompt_ids)})
                     if req.n_probs > 0:           # the entries recorded since the last event (a multi-byte piece may span tokens)
                         new, sent[0] = req.probs[sent[0]:], len(req.probs)
                         if openai:
-                            obj["choices"][0]["logprobs"] = openai_logprobs(new)
+                            obj["choices"][0]["logprobs"] = {"content": _logprob_items(new)}
                         else:
-                            obj["completion_probabilities"] = native_probs(new)
+                            obj["completion_probabilities"] = new
                     return b"data: " + json.dumps(obj).encode() + b"\n\n"
                 if kind == "done":
-                    obj = ({"id": rid, "object": "text_completion", "choices": [{"index": 0, "text": "", "finish_reason": content}]}
-                           if openai else {"content": "", "stop": True, "stop_type": content, "timings": req.timings()})
+                    if openai:
+                        obj = self._openai_text(req, rid)
+                        obj["choices"][0].update(text="", logprobs=None, finish_reason=content)
+                    else:
+                        obj = self._native_final(req, d, content="")
                     return b"data: " + json.dumps(obj).encode() + b"\n\n" + (b"data: [DONE]\n\n" if openai else b"")
                 return None
 
             await self._stream_request(req, writer, fmt)
             return False
         await self._run_blocking(req)
-        if openai:
-            await self._json(writer, {"id": rid, "object": "text_completion", "created": int(time.time()), "model": self.info.get("name", "model"),
-                                      "choices": [{"index": 0, "text": req.text, "finish_reason": req.finish_reason,
-                                                   **({"logprobs": openai_logprobs(req.probs)} if req.n_probs > 0 else {})}],
-                                      "usage": {"prompt_tokens": len(req.prompt_ids), "completion_tokens": len(req.output_ids),
-                                                "total_tokens": len(req.prompt_ids) + len(req.output_ids)}})
-        else:
-            await self._json(writer, {"content": req.text, "stop": True, "stop_type": req.finish_reason, "tokens_predicted": len(req.output_ids),
-                                      "tokens_evaluated": len(req.prompt_ids), "timings": req.timings(),
-                                      **({"completion_probabilities": native_probs(req.probs)} if req.n_probs > 0 else {})})
+        await self._json(writer, self._openai_text(req, rid) if openai else self._native_final(req, d))
         return True
 
     async def rerank(self, d: dict, writer) -> bool:
@@ -492,33 +603,42 @@ class Orchestrator:
                                   "usage": {"prompt_tokens": n_tok, "total_tokens": n_tok}, "results": results})
         return True
 
-    async def chat_completions(self, d: dict, writer) -> bool:
+    async def chat_completions(self, d, writer) -> bool:
         from . import toolcall
+        if not isinstance(d, dict) or not isinstance(d.get("messages"), list):
+            await self._json(writer, *self._bad_request("Expected 'messages' to be an array"))
+            return True
         tools = d.get("tools") or []
         setup = toolcall.prepare(d.get("messages", []), tools, d.get("tool_choice", "auto"), bool(d.get("parallel_tool_calls", False)))
         prompt = apply_chat_template(self.info.get("metadata", {}), setup.messages)
-        n_predict = int(d.get("max_tokens", d.get("max_completion_tokens", self.n_predict)))
+        n_predict = _as(int, d.get("max_tokens", d.get("max_completion_tokens")), self.n_predict)
+        n_predict = self.sched.eng.n_ctx if n_predict == -1 else max(1, n_predict)
         stop = d.get("stop") or []
         sampling = self._sampling_from(d)
         if setup.active and sampling.json_schema is None and not sampling.grammar:
             sampling.json_schema = setup.json_schema         # the generic tool-call envelope (common/chat.cpp, generic handler)
         req = Request(prompt=prompt, n_predict=n_predict, sampling=sampling, stop=[stop] if isinstance(stop, str) else list(stop),
-                      n_probs=max(1, int(d.get("top_logprobs") or 0)) if d.get("logprobs") else 0)
+                      n_probs=max(1, _as(int, d.get("top_logprobs"), 0)) if d.get("logprobs") else 0)
         rid = "chatcmpl-" + uuid.uuid4().hex[:24]
 
-        def chat_logprobs(items):     # OpenAI chat `logprobs.content`
-            def ent(t):
-                return {"token": t["token"], "logprob": t["logprob"], "bytes": list(t["token"].encode("utf-8"))}
-            return {"content": [{**ent(p), "top_logprobs": [ent(t) for t in p["top_logprobs"]]} for p in items]}
+        def chat_logprobs(items):     # OpenAI chat `logprobs.content` (llama-server adds the token id to each entry)
+            return {"content": _logprob_items(items)}
         model = self.info.get("name", "model")
         if d.get("stream"):
             writer.write(self._head("200 OK", [("content-type", "text/event-stream"), ("cache-control", "no-cache")] + CORS + [("connection", "close")]))
             held: list[str] = []
 
-            def chunk(delta, finish):
-                base = {"id": rid, "object": "chat.completion.chunk", "created": int(time.time()), "model": model,
-                        "choices": [{"index": 0, "delta": delta, "finish_reason": finish}]}
-                return b"data: " + json.dumps(base).encode() + b"\n\n"
+            opened = [False]
+
+            def chunk(delta, finish, **extra):
+                base = {"choices": [{"finish_reason": finish, "index": 0, "delta": delta}], "created": int(time.time()), "id": rid, "model": model,
+                        "system_fingerprint": FINGERPRINT, "object": "chat.completion.chunk", **extra}
+                out = b"data: " + json.dumps(base).encode() + b"\n\n"
+                if not opened[0]:             # the stream opens with the role, as the reference's does
+                    opened[0] = True
+                    if "role" not in delta:
+                        out = chunk({"role": "assistant", "content": None}, None) + out
+                return out
 
             def fmt(kind, content):
                 if kind == "token":
@@ -536,7 +656,7 @@ class Orchestrator:
                             reason = "tool_calls"
                         if msg.content:
                             out += chunk({"content": msg.content}, None)
-                    return out + chunk({}, reason) + b"data: [DONE]\n\n"
+                    return out + chunk({}, reason, timings=req.timings()) + b"data: [DONE]\n\n"
                 return None
 
             await self._stream_request(req, writer, fmt)
@@ -548,7 +668,7 @@ class Orchestrator:
             message = msg.to_openai()
             if msg.tool_calls:
                 reason = "tool_calls"
-        await self._json(writer, {"id": rid, "object": "chat.completion", "created": int(time.time()), "model": model,
+        await self._json(writer, {"id": rid, "object": "chat.completion", "created": int(time.time()), "model": model, "system_fingerprint": FINGERPRINT,
                                   "choices": [{"index": 0, "message": message, "finish_reason": reason,
                                                **({"logprobs": chat_logprobs(req.probs)} if req.n_probs > 0 else {})}],
                                   "usage": {"prompt_tokens": len(req.prompt_ids), "completion_tokens": len(req.output_ids),

@@ -248,8 +248,11 @@ class Sampler:
 
     def _pick(self, row: torch.Tensor) -> int:
         p = self.p
+        self.last_dist = None          # (token ids, probabilities) the token was finally drawn from (`post_sampling_probs`)
         if p.greedy:
-            return int(row.argmax())
+            tok = int(row.argmax())
+            self.last_dist = (torch.tensor([tok]), torch.tensor([1.0]))
+            return tok
         if p.top_n_sigma > 0:
             row = row.masked_fill(row < row.max() - p.top_n_sigma * row.std(), float("-inf"))
         if p.mirostat == 1:
@@ -280,6 +283,7 @@ class Sampler:
             probs = probs / probs.sum()
             tok = int(torch.multinomial(probs, 1, generator=self.gen))
             self.mu -= p.mirostat_eta * (float(-torch.log2(probs[tok])) - p.mirostat_tau)
+            self.last_dist = (torch.arange(probs.numel()), probs)
             return tok
         vals, ids = filter_candidates(row, p.top_k, p.top_p, p.min_p, p.typical_p)
         ok = torch.isfinite(vals)
@@ -299,6 +303,7 @@ class Sampler:
                 keep[above[:-1]] = False
                 probs = torch.where(keep, probs, torch.zeros_like(probs))
                 probs = probs / probs.sum()
+        self.last_dist = (ids, probs)
         return int(ids[torch.multinomial(probs, 1, generator=self.gen)])
 
     def sample(self, logits: torch.Tensor) -> int:

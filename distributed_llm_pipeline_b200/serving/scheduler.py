@@ -41,6 +41,7 @@ class Request:
     cache_prompt: bool = True
     n_keep: int = 0             # tokens of the prompt that survive a context shift (-1 = the whole prompt)
     n_probs: int = 0            # > 0: record the log-probability of every generated token and of the n_probs most likely ones
+    post_sampling_probs: bool = False   # record the probabilities the token was drawn from (after the sampler chain) instead
     n_draft: int = 0            # > 0: speculative decoding with prompt-lookup drafts of up to this many tokens (greedy requests)
     id: int = 0
     # filled in by the scheduler
@@ -49,6 +50,11 @@ class Request:
     probs: list[dict] = field(default_factory=list)       # per generated token: {"id", "token", "logprob", "top_logprobs": [...]}
     text: str = ""
     finish_reason: str | None = None
+    stop_type: str = "none"     # llama-server's name for it: "none" | "eos" | "limit" | "word"
+    stopping_word: str = ""
+    truncated: bool = False     # generation ended because the context was full
+    id_slot: int = -1
+    tokens_cached: int = 0      # tokens of this request resident in the slot's cache when it ended
     t_submit: float = 0.0
     t_start: float = 0.0
     t_first_token: float = 0.0
@@ -64,8 +70,9 @@ class Request:
         n_gen = max(0, len(self.output_ids) - 1)
         return {
             "prompt_n": self.n_prompt_processed, "cache_n": self.n_prompt_cached, "prompt_ms": round(p_ms, 3),
+            "prompt_per_token_ms": round(p_ms / max(1, self.n_prompt_processed), 4),
             "prompt_per_second": round(self.n_prompt_processed / p_ms * 1e3, 2) if p_ms else 0.0,
-            "predicted_n": len(self.output_ids), "predicted_ms": round(g_ms, 3),
+            "predicted_n": len(self.output_ids), "predicted_ms": round(g_ms, 3), "predicted_per_token_ms": round(g_ms / max(1, n_gen), 4),
             "predicted_per_second": round(n_gen / g_ms * 1e3, 2) if g_ms and n_gen else 0.0,
             "ttft_ms": round((self.t_first_token - self.t_submit) * 1e3, 3) if self.t_first_token else None,
         }
@@ -417,8 +424,22 @@ class Scheduler:
                 lp = torch.log_softmax(rows[i], -1)      # (server-context.cpp populate_token_probs, post_sampling_probs = false)
                 top = lp.topk(min(s.req.n_probs, lp.numel()))
                 txt = self.tok.token_texts()
-                s.req.probs.append({"id": tok, "token": txt[tok] or "", "logprob": float(lp[tok]),
-                                    "top_logprobs": [{"id": int(j), "token": txt[int(j)] or "", "logprob": float(v)} for v, j in zip(top.values, top.indices)]})
+
+                def entry(j, **val):
+                    return {"id": int(j), "token": txt[int(j)] or "", "bytes": list(self.tok.token_bytes(int(j))), **val}
+                dist = getattr(s.sampler, "last_dist", None)
+                if s.req.post_sampling_probs and dist is not None:
+                    # the distribution the token was drawn from; padded with the likeliest other tokens at probability 0
+                    ids, pr = dist
+                    order = torch.argsort(pr, descending=True, stable=True)[:s.req.n_probs]
+                    cand = [(int(ids[k]), float(pr[k])) for k in order]
+                    seen = {j for j, _ in cand}
+                    cand += [(int(j), 0.0) for j in lp.topk(min(2 * s.req.n_probs + 1, lp.numel())).indices if int(j) not in seen][:s.req.n_probs - len(cand)]
+                    chosen = next((q for j, q in zip(ids.tolist(), pr.tolist()) if j == tok), 0.0)
+                    s.req.probs.append({**entry(tok, prob=chosen, logprob=float(lp[tok])), "top_probs": [entry(j, prob=q) for j, q in cand]})
+                else:
+                    s.req.probs.append({**entry(tok, logprob=float(lp[tok])),
+                                        "top_logprobs": [entry(j, logprob=float(v)) for v, j in zip(top.values, top.indices)]})
             out.append(tok)
         return out
 
@@ -439,13 +460,16 @@ class Scheduler:
                     if cut > emitted:
                         self._emit(req, "token", req.text[emitted:cut])
                     req.text = req.text[:cut]
+                    req.stop_type, req.stopping_word = "word", hit
                     self._finish(s, "stop")
                     return
                 self._emit(req, "token", piece)
         if is_stop:
             req.output_ids.pop()
+            req.stop_type = "eos"
             self._finish(s, "stop")
         elif len(req.output_ids) >= req.n_predict:
+            req.stop_type = "limit"
             self._finish(s, "length")
         elif s.n_past + 1 >= self.eng.n_ctx:
             if self.context_shift and hasattr(self.eng, "shift_seq"):
@@ -459,6 +483,7 @@ class Scheduler:
                 self.metrics.add(context_shifts_total=1)
                 self._emit(req, "log", f"slot {s.idx}: context shift, kept {n_keep}, discarded {n_discard} tokens\n")
             else:
+                req.stop_type, req.truncated = "limit", True
                 self._finish(s, "length")  # context full (the reference stops as well unless --context-shift)
 
     def _finish(self, s: Slot, reason: str):
@@ -469,6 +494,7 @@ class Scheduler:
             self._emit(req, "token", tail)
         req.finish_reason = reason
         req.t_done = time.time()
+        req.id_slot, req.tokens_cached = s.idx, s.n_past
         t = req.timings()
         self._emit(req, "log", f"slot {s.idx}: request {req.id} done ({reason}) | prompt eval {t['prompt_n']} tok "
                                f"{t['prompt_per_second']} tok/s | eval {t['predicted_n']} tok {t['predicted_per_second']} tok/s\n")

@@ -310,6 +310,16 @@ class Tokenizer:
             self._texts = out
         return self._texts
 
+    def decode_with_specials(self, ids: list[int]) -> str:
+        """Text with control tokens written out (`<s> one two`), nothing stripped: what llama-server reports as the `prompt` it ran."""
+        out = bytearray()
+        for i in ids:
+            if 0 <= i < self.n_vocab and self.types[i] in (TokenType.CONTROL, TokenType.USER_DEFINED):
+                out += self.tokens[i].encode("utf-8")
+            else:
+                out += self.token_bytes(i)
+        return out.decode("utf-8", errors="replace")
+
     def decode(self, ids: list[int], strip_leading_space: bool = True) -> str:
         data = b"".join(self.token_bytes(i) for i in ids)
         s = data.decode("utf-8", errors="replace")
@@ -341,12 +351,9 @@ class StreamDecoder:
                 cut = len(self.pending) - back
             break
         out, self.pending = self.pending[:cut], self.pending[cut:]
-        s = out.decode("utf-8", errors="replace")
-        if self.first and s:
-            if self.tok.model == "llama" and self.tok.add_space_prefix and s.startswith(" "):
-                s = s[1:]
-            self.first = False
-        return s
+        # (a generated piece keeps its leading space - "one" + " two" - exactly as the reference's token_to_piece gives it to llama-cli
+        # and llama-server; only detokenising a whole sequence, `Tokenizer.decode`, drops the space the SPM prefix rule added)
+        return out.decode("utf-8", errors="replace")
 
     def flush(self) -> str:
         s = self.pending.decode("utf-8", errors="replace")

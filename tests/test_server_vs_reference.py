@@ -130,13 +130,14 @@ def test_logit_bias_grammar_and_stop_agree(pair):
             assert isinstance(v["ok"], bool) and v["n"] in (1, 2, 3)
         else:
             assert d["content"].lstrip().startswith("{")
-    assert a["stop_type"] == "stop" and json.loads(a["content"])["n"] in (1, 2, 3)       # ours bounds every repetition, so it always closes
+    assert a["stop_type"] == "eos" and json.loads(a["content"])["n"] in (1, 2, 3)       # ours bounds every repetition, so it always closes
     # a stop string cuts both answers at the same place and is reported the same way
     base = _post(ref, "/completion", {"prompt": "hello there", "n_predict": 8, "temperature": 0, "cache_prompt": False})["content"]
     stop = base[3:5]
     a = _post(ours, "/completion", {"prompt": "hello there", "n_predict": 8, "temperature": 0, "cache_prompt": False, "stop": [stop]})
     b = _post(ref, "/completion", {"prompt": "hello there", "n_predict": 8, "temperature": 0, "cache_prompt": False, "stop": [stop]})
-    assert a["content"] == b["content"] == base[:base.index(stop)] and a["stop_type"] == "stop" and b["stop_type"] == "word"
+    assert a["content"] == b["content"] == base[:base.index(stop)] and a["stop_type"] == b["stop_type"] == "word"
+    assert a["stopping_word"] == b["stopping_word"] == stop and a["truncated"] is b["truncated"] is False
 
 
 def test_openai_envelope_and_meta_routes_agree(pair):
@@ -380,3 +381,89 @@ def test_zz_metrics_and_slots_agree(pair):
             "top_n_sigma", "dynatemp_range", "dynatemp_exponent", "n_predict", "max_tokens", "n_keep", "ignore_eos", "n_probs", "stream", "lora",
             "speculative.n_max"} <= shared
     assert set(served_a[0]["next_token"][0]) == set(served_b[0]["next_token"][0])
+
+
+def _keys(d, pre=""):
+    out = set()
+    if isinstance(d, dict):
+        for k, v in d.items():
+            out.add(pre + k)
+            out |= _keys(v, pre + k + ".")
+    elif isinstance(d, list) and d:
+        out |= _keys(d[0], pre + "[].")
+    return out
+
+
+def _status(port, path, body):
+    r = urllib.request.Request(f"http://127.0.0.1:{port}{path}", json.dumps(body).encode(), {"Content-Type": "application/json"})
+    try:
+        return 200, json.loads(urllib.request.urlopen(r, timeout=60).read())
+    except urllib.error.HTTPError as e:
+        return e.code, json.loads(e.read())
+
+
+def test_response_envelopes_carry_every_field_of_the_reference(pair):
+    """Field for field: whatever key the reference puts into an answer (closing record of /completion with its generation_settings, stream events,
+    token probabilities before and after the sampler chain, both OpenAI dialects, /tokenize with pieces, an array of prompts) is in ours too, the
+    deterministic values are equal, and malformed requests are refused with the same status, code and type instead of a dropped connection."""
+    ours, ref = pair
+    cases = [("/completion", {"prompt": "one two three", "n_predict": 4, "temperature": 0, "return_tokens": True, "cache_prompt": False}),
+             ("/completion", {"prompt": [5, 9, 200, 33], "n_predict": 3, "temperature": 0, "cache_prompt": False}),
+             ("/completion", {"prompt": ["one two", "three four"], "n_predict": 3, "temperature": 0, "cache_prompt": False}),
+             ("/completion", {"prompt": "one", "n_predict": 3, "temperature": 0, "n_probs": 2, "cache_prompt": False}),
+             ("/completion", {"prompt": "one", "n_predict": 3, "temperature": 0, "n_probs": 2, "post_sampling_probs": True, "cache_prompt": False}),
+             ("/completion", {"prompt": "one two three", "n_predict": 0, "temperature": 0, "cache_prompt": False}),       # still one token, as there
+             ("/v1/completions", {"prompt": "one two three", "max_tokens": 4, "temperature": 0}),
+             ("/v1/completions", {"prompt": "one two three", "max_tokens": 4, "temperature": 0, "logprobs": 2}),
+             ("/v1/chat/completions", {"messages": [{"role": "user", "content": "hi"}], "max_tokens": 4, "temperature": 0, "logprobs": True, "top_logprobs": 2}),
+             ("/tokenize", {"content": "hello wörld", "with_pieces": True}), ("/tokenize", {"content": "hello", "add_special": True})]
+    for path, body in cases:
+        (sa, a), (sb, b) = _status(ours, path, body), _status(ref, path, body)
+        assert sa == sb == 200, (path, body, a, b)
+        assert _keys(b) - _keys(a) == set(), (path, body, sorted(_keys(b) - _keys(a)))
+        if isinstance(b, list):       # an array of prompts: one record each (the reference lists them as they finish: pair them by prompt)
+            assert len(a) == len(b) == len(body["prompt"]) and sorted(x["index"] for x in a) == sorted(y["index"] for y in b)
+            a, b = sorted(a, key=lambda r: r["prompt"]), sorted(b, key=lambda r: r["prompt"])
+        for x, y in zip(a if isinstance(a, list) else [a], b if isinstance(b, list) else [b]):
+            for k in ("content", "tokens", "stop", "stop_type", "stopping_word", "truncated", "tokens_predicted", "tokens_evaluated", "prompt", "has_new_line") + \
+                    (() if isinstance(b, list) else ("index",)):
+                if k in y:
+                    assert x[k] == y[k], (path, body, k, x[k], y[k])
+            if "completion_probabilities" in y:
+                for p, q in zip(x["completion_probabilities"], y["completion_probabilities"]):
+                    assert (p["id"], p["token"], p["bytes"]) == (q["id"], q["token"], q["bytes"])
+                    tp, tq = p.get("top_logprobs", p.get("top_probs")), q.get("top_logprobs", q.get("top_probs"))
+                    assert [t["id"] for t in tp] == [t["id"] for t in tq]
+                    for t, u in zip(tp, tq):
+                        assert abs(t.get("logprob", t.get("prob")) - u.get("logprob", u.get("prob"))) < 2e-2
+            if path.startswith("/v1/"):
+                assert x["choices"][0]["finish_reason"] == y["choices"][0]["finish_reason"] and x["usage"] == y["usage"] and x["object"] == y["object"]
+                la, lb = x["choices"][0].get("logprobs"), y["choices"][0].get("logprobs")
+                assert (la is None) == (lb is None)
+                if lb:
+                    assert [e["id"] for e in la["content"]] == [e["id"] for e in lb["content"]]
+        if path == "/tokenize":
+            assert a == b
+    # streams: the same keys in the token events and in the closing event
+    for path, body in [("/completion", {"prompt": "one", "n_predict": 2, "temperature": 0, "stream": True, "cache_prompt": False}),
+                       ("/v1/chat/completions", {"messages": [{"role": "user", "content": "hi"}], "max_tokens": 2, "temperature": 0, "stream": True})]:
+        ev = {}
+        for port in (ours, ref):
+            r = urllib.request.Request(f"http://127.0.0.1:{port}{path}", json.dumps(body).encode(), {"Content-Type": "application/json"})
+            ev[port] = [json.loads(ln[6:]) for ln in urllib.request.urlopen(r, timeout=60).read().decode().split("\n") if ln.startswith("data: {")]
+        assert len(ev[ours]) == len(ev[ref]) >= 3
+        for x, y in zip(ev[ours], ev[ref]):
+            assert _keys(y) - _keys(x) == set(), (path, sorted(_keys(y) - _keys(x)))
+            if "content" in y:
+                assert (x["content"], x["tokens"], x["stop"]) == (y["content"], y["tokens"], y["stop"])
+            else:
+                assert x["choices"][0]["delta"] == y["choices"][0]["delta"] and x["choices"][0]["finish_reason"] == y["choices"][0]["finish_reason"]
+    # malformed requests
+    for path, body in [("/completion", {"n_predict": 3}), ("/completion", "notadict"), ("/v1/chat/completions", {"messages": "hi"}),
+                       ("/v1/chat/completions", {"max_tokens": 3})]:
+        (sa, a), (sb, b) = _status(ours, path, body), _status(ref, path, body)
+        assert sa == sb == 400 and a["error"]["code"] == b["error"]["code"] == 400 and a["error"]["type"] == b["error"]["type"], (path, body, a, b)
+    # values of the wrong type fall back to the defaults on both sides; the request is served
+    for body in [{"prompt": "one", "n_predict": 2, "temperature": "hot", "top_k": None, "seed": "x"}, {"prompt": "one", "n_predict": "many", "max_tokens": 2}]:
+        (sa, a), (sb, b) = _status(ours, "/completion", body), _status(ref, "/completion", body)
+        assert sa == sb == 200 and a["stop"] is b["stop"] is True
