@@ -188,7 +188,7 @@ class Orchestrator:
                                                        ("content-length", "0")]))
             await writer.drain()
             return True
-        is_api = method == "POST" or path in ("/metrics", "/slots", "/props", "/v1/models", "/api/tags") or path.startswith("/slots/")
+        is_api = method == "POST" or path in ("/metrics", "/slots", "/props", "/v1/models", "/models", "/api/tags", "/lora-adapters") or path.startswith("/slots/")
         if self.api_key and is_api and path != "/health":
             auth = headers.get("authorization", "")
             if auth != f"Bearer {self.api_key}" and headers.get("x-api-key", "") != self.api_key:
@@ -220,7 +220,36 @@ class Orchestrator:
                 return await self.completion(d, writer)
             if method == "POST" and path in ("/completion", "/completions", "/v1/completions"):
                 return await self.completion(json.loads(body or b"{}"), writer, openai=path.startswith("/v1"))
-            if method == "POST" and path == "/v1/chat/completions":
+            if method == "POST" and path == "/v1/messages/count_tokens":     # the prompt the messages render to, tokenised
+                prompt = apply_chat_template(self.info.get("metadata", {}), self._anthropic_to_messages(json.loads(body or b"{}")))
+                await self._json(writer, {"input_tokens": len(self.sched.tok.encode(prompt))})
+                return True
+            if method == "POST" and path == "/api/show":                      # Ollama: what is loaded
+                md = self.info.get("metadata", {})
+                await self._json(writer, {"model_info": {f"{self.info.get('arch', 'llama')}.context_length": self.sched.eng.n_ctx}, "modelfile": "", "parameters": "",
+                                          "template": md.get("tokenizer.chat_template", ""), "details": self._ollama_details(), "capabilities": ["completion"]})
+                return True
+            if path == "/lora-adapters" and method in ("GET", "POST"):
+                cur = self.info.get("lora", [])
+                if method == "GET":
+                    await self._json(writer, cur)
+                    return True
+                want = json.loads(body or b"[]")
+                asked = {int(x.get("id", -1)): float(x.get("scale", 0.0)) for x in want if isinstance(x, dict)} if isinstance(want, list) else None
+                if asked is None or any(i not in {a["id"] for a in cur} for i in asked):
+                    await self._json(writer, *self._bad_request("expected an array of {id, scale} naming loaded adapters"))
+                elif any(abs(asked.get(a["id"], 0.0) - a["scale"]) > 1e-9 for a in cur):
+                    # adapters are folded into the weights when the model is loaded (models/weights.py): another scale needs a reload
+                    await self._json(writer, {"error": {"code": 501, "message": "adapter scales are applied at load time here: restart with --lora path:scale",
+                                                        "type": "not_supported_error"}}, "501 Not Implemented")
+                else:
+                    await self._json(writer, {"success": True})
+                return True
+            if method == "POST" and path == "/props":
+                await self._json(writer, {"error": {"code": 501, "message": "this server's properties are fixed at start-up", "type": "not_supported_error"}},
+                                 "501 Not Implemented")
+                return True
+            if method == "POST" and path in ("/v1/chat/completions", "/chat/completions"):
                 return await self.chat_completions(json.loads(body or b"{}"), writer)
             if method == "POST" and path in ("/api/generate", "/api/chat"):
                 return await self.ollama(path, json.loads(body or b"{}"), writer)
@@ -264,7 +293,7 @@ class Orchestrator:
                 return True
             if method == "POST" and path in ("/rerank", "/reranking", "/v1/rerank", "/v1/reranking"):
                 return await self.rerank(json.loads(body or b"{}"), writer)
-            if method == "GET" and path == "/health":
+            if method == "GET" and path in ("/health", "/v1/health"):
                 await self._json(writer, {"status": "ok"})
                 return True
             if method == "GET" and path == "/metrics":
@@ -294,9 +323,13 @@ class Orchestrator:
                     # this server's own fields
                     "model": self.info, "n_ctx": self.sched.eng.n_ctx, "uptime_s": round(time.time() - self.t_start, 1)})
                 return True
-            if method == "GET" and path == "/v1/models":
-                await self._json(writer, {"object": "list", "data": [{"id": self.info.get("name", "model"), "object": "model",
-                                                                        "created": int(self.t_start), "owned_by": "dlp_b200"}]})
+            if method == "GET" and path in ("/v1/models", "/models"):          # the OpenAI list and the Ollama list in one answer, as the reference gives it
+                name = self.info.get("name", "model")
+                await self._json(writer, {"models": [{"name": name, "model": name, "modified_at": "", "size": "", "digest": "", "type": "model", "description": "",
+                                                      "tags": [""], "capabilities": ["completion"], "parameters": "", "details": self._ollama_details()}],
+                                          "object": "list", "data": [{"id": name, "object": "model", "created": int(self.t_start), "owned_by": "dlp_b200",
+                                                                      "meta": {"n_vocab": self.info.get("n_vocab"), "n_ctx_train": self.info.get("n_ctx_train"),
+                                                                               "n_embd": self.info.get("n_embd"), "n_params": self.info.get("n_params")}}]})
                 return True
             if method in ("GET", "HEAD"):
                 return await self.static(path, writer, head=(method == "HEAD"))
@@ -459,6 +492,10 @@ class Orchestrator:
                               min_p=_as(float, d.get("min_p"), 0.05), typical_p=_as(float, d.get("typical_p"), 1.0),
                               repeat_penalty=_as(float, d.get("repeat_penalty"), 1.0), frequency_penalty=_as(float, d.get("frequency_penalty"), 0.0),
                               presence_penalty=_as(float, d.get("presence_penalty"), 0.0), seed=max(0, _as(int, d.get("seed"), 0)))
+
+    def _ollama_details(self) -> dict:
+        return {"parent_model": "", "format": "gguf", "family": self.info.get("arch", ""), "families": [self.info.get("arch", "")], "parameter_size": "",
+                "quantization_level": ""}
 
     def _bad_request(self, message: str) -> tuple[dict, str]:
         return {"error": {"code": 400, "message": message, "type": "invalid_request_error"}}, "400 Bad Request"
@@ -711,15 +748,19 @@ class Orchestrator:
         await self._json(writer, obj(req.text, True, req.finish_reason))
         return True
 
-    async def anthropic_messages(self, d: dict, writer) -> bool:
-        msgs = list(d.get("messages", []))
+    @staticmethod
+    def _anthropic_to_messages(d: dict) -> list[dict]:
         norm = []
         if d.get("system"):
             sys_txt = d["system"] if isinstance(d["system"], str) else "".join(b.get("text", "") for b in d["system"])
             norm.append({"role": "system", "content": sys_txt})
-        for m in msgs:
+        for m in list(d.get("messages", [])):
             c = m.get("content", "")
             norm.append({"role": m.get("role", "user"), "content": c if isinstance(c, str) else "".join(b.get("text", "") for b in c)})
+        return norm
+
+    async def anthropic_messages(self, d: dict, writer) -> bool:
+        norm = self._anthropic_to_messages(d)
         stop = d.get("stop_sequences") or []
         req = Request(prompt=apply_chat_template(self.info.get("metadata", {}), norm), n_predict=int(d.get("max_tokens", self.n_predict)),
                       sampling=self._sampling_from(d), stop=list(stop))
@@ -855,16 +896,34 @@ class ModelRouter(Orchestrator):
                     self._unload(n)
 
     async def route(self, method, path, headers, body, reader, writer) -> bool:
-        if method == "GET" and path == "/v1/models":
+        if method == "POST" and path in ("/models/load", "/models/unload"):      # llama-server router mode (server-models.cpp): explicit load / unload
+            try:
+                name = str(json.loads(body or b"{}").get("model", ""))
+            except (json.JSONDecodeError, AttributeError):
+                name = ""
+            if name not in self.models:
+                await self._json(writer, {"error": {"code": 404, "message": f"model {name!r} not found", "type": "not_found_error"}}, "404 Not Found")
+            elif path == "/models/load":
+                await self.acquire(name)
+                await self._json(writer, {"success": True})
+            else:
+                async with self._load_lock:
+                    if name in self.loaded and self._busy(self.loaded[name]):
+                        await self._json(writer, {"error": {"code": 409, "message": f"model {name!r} is serving requests", "type": "unavailable_error"}}, "409 Conflict")
+                        return True
+                    self._unload(name)
+                await self._json(writer, {"success": True})
+            return True
+        if method == "GET" and path in ("/v1/models", "/models"):
             await self._json(writer, {"object": "list", "data": [
                 {"id": n, "object": "model", "owned_by": "dlp_b200", "path": p,
                  "status": "loaded" if n in self.loaded else "unloaded"} for n, p in self.models.items()]})
             return True
-        if method == "GET" and path == "/health":
+        if method == "GET" and path in ("/health", "/v1/health"):
             await self._json(writer, {"status": "ok", "models_loaded": sorted(self.loaded), "loads": self.n_loads, "replicas": self.replicas,
                                       "in_flight": {n: [self._in_flight(o) for o in g] for n, g in self.loaded.items()}})
             return True
-        if method in ("GET", "HEAD", "OPTIONS") and path not in ("/metrics", "/slots", "/props"):
+        if method in ("GET", "HEAD", "OPTIONS") and path not in ("/metrics", "/slots", "/props", "/lora-adapters"):
             return await super().route(method, path, headers, body, reader, writer)
         name = next(iter(self.models))
         if body:
@@ -987,7 +1046,9 @@ def build_service(model: str, device: str = "cuda", n_ctx: int = 2048, n_slots: 
     info = {"name": str(f.metadata.get("general.name", os.path.basename(model))), "n_params": cfg.n_params(), "n_ctx_train": cfg.n_ctx_train,
             "metadata": {"tokenizer.chat_template": f.metadata.get("tokenizer.chat_template", ""),
                          "bos_token": tok.tokens[tok.bos_id] if 0 <= tok.bos_id < tok.n_vocab else "",
-                         "eos_token": tok.tokens[tok.eos_id] if 0 <= tok.eos_id < tok.n_vocab else ""}, **info_extra}
+                         "eos_token": tok.tokens[tok.eos_id] if 0 <= tok.eos_id < tok.n_vocab else ""}, **info_extra,
+            "arch": cfg.arch, "n_vocab": tok.n_vocab, "n_embd": cfg.n_embd, "path": model,
+            "lora": [{"id": i, "path": getattr(a, "path", str(a)), "scale": float(getattr(a, "scale", 1.0))} for i, a in enumerate(lora or [])]}
     draft_eng = None
     if model_draft:
         fd = open_gguf(model_draft)

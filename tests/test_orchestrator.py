@@ -275,8 +275,15 @@ def test_model_router_loads_on_demand_and_unloads_lru(tmp_models):
     assert json.loads(body)["content"] == first
     st, _, _ = _http(port, "POST", "/completion", req("nope"))
     assert " 404 " in st
+    # explicit unload / load (llama-server router mode: POST /models/unload, /models/load)
+    assert json.loads(_http(port, "POST", "/models/unload", json.dumps({"model": "llama-tiny"}).encode())[2]) == {"success": True}
+    assert json.loads(_http(port, "GET", "/health")[2])["models_loaded"] == []
+    assert json.loads(_http(port, "POST", "/models/load", json.dumps({"model": "qwen-tiny"}).encode())[2]) == {"success": True}
+    assert json.loads(_http(port, "GET", "/v1/health")[2])["models_loaded"] == ["qwen-tiny"]
+    assert " 404 " in _http(port, "POST", "/models/load", json.dumps({"model": "nope"}).encode())[0]
+    _http(port, "POST", "/completion", req("llama-tiny"))
     _, _, body = _http(port, "GET", "/health")
-    assert json.loads(body)["loads"] == 3
+    assert json.loads(body)["loads"] == 5
     deadline = time.time() + 10                                                   # --sleep-idle-seconds: unloaded when idle
     while time.time() < deadline:
         _, _, body = _http(port, "GET", "/health")

@@ -467,3 +467,30 @@ def test_response_envelopes_carry_every_field_of_the_reference(pair):
     for body in [{"prompt": "one", "n_predict": 2, "temperature": "hot", "top_k": None, "seed": "x"}, {"prompt": "one", "n_predict": "many", "max_tokens": 2}]:
         (sa, a), (sb, b) = _status(ours, "/completion", body), _status(ref, "/completion", body)
         assert sa == sb == 200 and a["stop"] is b["stop"] is True
+
+
+def test_the_remaining_routes_answer_like_the_reference(pair):
+    """Every route `llama-server` registers (tools/server/server.cpp) exists here: the aliases without `/v1`, `/v1/health`, the combined model
+    list, Ollama's `/api/show`, `/lora-adapters`, and the Anthropic token counter - same keys, same counts."""
+    ours, ref = pair
+
+    def call(port, method, path, body=None):
+        r = urllib.request.Request(f"http://127.0.0.1:{port}{path}", json.dumps(body).encode() if body is not None else None,
+                                   {"Content-Type": "application/json"}, method=method)
+        try:
+            return 200, json.loads(urllib.request.urlopen(r, timeout=60).read())
+        except urllib.error.HTTPError as e:
+            return e.code, json.loads(e.read())
+    msgs = [{"role": "user", "content": "hello there"}]
+    for method, path, body in [("GET", "/v1/health", None), ("GET", "/models", None), ("GET", "/v1/models", None), ("POST", "/api/show", {"name": "x"}),
+                               ("GET", "/lora-adapters", None), ("POST", "/lora-adapters", []), ("POST", "/v1/messages/count_tokens", {"messages": msgs}),
+                               ("POST", "/chat/completions", {"messages": msgs, "max_tokens": 2, "temperature": 0}),
+                               ("POST", "/v1/messages", {"messages": msgs, "max_tokens": 3, "temperature": 0})]:
+        (sa, a), (sb, b) = call(ours, method, path, body), call(ref, method, path, body)
+        assert sa == sb == 200, (path, a, b)
+        assert _keys(b) - _keys(a) - {"data.[].meta.vocab_type", "data.[].meta.size"} == set(), (path, sorted(_keys(b) - _keys(a)))
+    assert call(ours, "POST", "/v1/messages/count_tokens", {"messages": msgs})[1] == call(ref, "POST", "/v1/messages/count_tokens", {"messages": msgs})[1]
+    a, b = call(ours, "POST", "/v1/messages", {"messages": msgs, "max_tokens": 3, "temperature": 0})[1], call(ref, "POST", "/v1/messages", {"messages": msgs, "max_tokens": 3, "temperature": 0})[1]
+    assert a["content"] == b["content"] and a["usage"] == b["usage"] and a["stop_reason"] == b["stop_reason"]
+    ma, mb = call(ours, "GET", "/models")[1]["data"][0]["meta"], call(ref, "GET", "/models")[1]["data"][0]["meta"]
+    assert all(ma[k] == mb[k] for k in ("n_vocab", "n_ctx_train", "n_embd", "n_params"))
