@@ -416,9 +416,10 @@ void handle_connection(int fd) {
             send_all(fd, h);
         } else if (rq.method == "POST" && rq.path == "/chat") {
             handle_chat(fd, rq);
-        } else if (rq.method == "GET" && (rq.path == "/health" || rq.path == "/metrics" || rq.path == "/slots")) {
+        } else if (rq.method == "GET" && (rq.path == "/health" || rq.path == "/v1/health" || rq.path == "/metrics" || rq.path == "/slots")) {
             proxy_get(fd, rq.path);
-        } else if (rq.method == "POST" || (rq.method == "GET" && (rq.path == "/props" || rq.path == "/v1/models"))) {
+        } else if (rq.method == "POST" || (rq.method == "GET" && (rq.path == "/props" || rq.path == "/v1/models" || rq.path == "/models" ||
+                                                                   rq.path == "/lora-adapters" || rq.path == "/api/tags"))) {
             proxy_http(fd, rq);
         } else if (rq.method == "GET" || rq.method == "HEAD") {
             serve_static(fd, rq);
