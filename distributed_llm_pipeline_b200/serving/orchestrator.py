@@ -37,7 +37,7 @@ def sse_event(msg_type: str, content: str) -> bytes:
 KEEPALIVE = b":\n\n"
 
 
-def _render_jinja(tmpl: str, messages: list[dict], meta: dict) -> str | None:
+def _render_jinja(tmpl: str, messages: list[dict], meta: dict, add_generation_prompt: bool = True) -> str | None:
     """Render the model's own Jinja chat template (what `common_chat_templates_apply` does through minja) in a sandbox; None when
     jinja2 is missing or the template does not render (the marker-based fall-backs below take over)."""
     try:
@@ -50,13 +50,13 @@ def _render_jinja(tmpl: str, messages: list[dict], meta: dict) -> str | None:
         def raise_exception(msg):
             raise ValueError(msg)
         env.globals["raise_exception"] = raise_exception
-        return env.from_string(tmpl).render(messages=messages, add_generation_prompt=True, bos_token=str(meta.get("bos_token", "")),
+        return env.from_string(tmpl).render(messages=messages, add_generation_prompt=add_generation_prompt, bos_token=str(meta.get("bos_token", "")),
                                             eos_token=str(meta.get("eos_token", "")))
     except Exception:      # noqa: BLE001 - any template problem falls back to the built-in formats
         return None
 
 
-def apply_chat_template(meta: dict, messages: list[dict]) -> str:
+def apply_chat_template(meta: dict, messages: list[dict], add_generation_prompt: bool = True) -> str:
     """Chat formatting, in the reference's order of preference (`common/chat.cpp`, `llama-chat.cpp`): a built-in format forced by name
     (`--chat-template NAME` -> `meta["dlp.chat_template_name"]`), the model's own Jinja template rendered in a sandbox, the built-in
     format its template text is recognised as (`serving/chat_templates.py`: 46 formats, each checked against the reference's output), and
@@ -64,15 +64,15 @@ def apply_chat_template(meta: dict, messages: list[dict]) -> str:
     from . import chat_templates
     name = meta.get("dlp.chat_template_name")
     if name:
-        return chat_templates.apply(str(name), messages)
+        return chat_templates.apply(str(name), messages, add_generation_prompt)
     tmpl = str(meta.get("tokenizer.chat_template", ""))
-    rendered = _render_jinja(tmpl, messages, meta) if "{%" in tmpl or "{{" in tmpl else None
+    rendered = _render_jinja(tmpl, messages, meta, add_generation_prompt) if "{%" in tmpl or "{{" in tmpl else None
     if rendered is not None:
         return rendered
     detected = chat_templates.detect(tmpl) if tmpl else None
     if detected:
-        return chat_templates.apply(detected, messages)
-    return chat_templates.apply("chatml", messages)
+        return chat_templates.apply(detected, messages, add_generation_prompt)
+    return chat_templates.apply("chatml", messages, add_generation_prompt)
 
 
 FINGERPRINT = "dlp_b200"
@@ -204,13 +204,16 @@ class Orchestrator:
             if method == "POST" and path.startswith("/slots/"):
                 return await self.slot_action(path, json.loads(body or b"{}"), writer)
             if method == "POST" and path == "/apply-template":
-                await self._json(writer, {"prompt": apply_chat_template(self.info.get("metadata", {}), json.loads(body or b"{}").get("messages", []))})
+                d = json.loads(body or b"{}")
+                await self._json(writer, {"prompt": apply_chat_template(self.info.get("metadata", {}), d.get("messages", []),
+                                                                        bool(d.get("add_generation_prompt", True)))})
                 return True
             if method == "POST" and path == "/infill":
                 d = json.loads(body or b"{}")
                 fim = self.sched.tok.fim_ids()
                 if fim is None:
-                    await self._json(writer, {"error": "the model's vocabulary has no fill-in-the-middle tokens"}, "501 Not Implemented")
+                    await self._json(writer, {"error": {"code": 501, "message": "Infill is not supported by this model", "type": "not_supported_error"}},
+                                     "501 Not Implemented")
                     return True
                 t = self.sched.tok
                 ids = [fim["pre"]] + t.encode(d.get("input_prefix", ""), add_bos=False) + [fim["suf"]] + \
@@ -308,18 +311,12 @@ class Orchestrator:
                 md = self.info.get("metadata", {})
                 await self._json(writer, {
                     "default_generation_settings": {"n_ctx": self.sched.eng.n_ctx, "params": {
-                        "seed": dp.seed, "temperature": dp.temperature, "dynatemp_range": dp.dynatemp_range, "dynatemp_exponent": dp.dynatemp_exponent,
-                        "top_k": dp.top_k, "top_p": dp.top_p, "min_p": dp.min_p, "top_n_sigma": dp.top_n_sigma, "xtc_probability": dp.xtc_probability,
-                        "xtc_threshold": dp.xtc_threshold, "typical_p": dp.typical_p, "repeat_last_n": dp.repeat_last_n, "repeat_penalty": dp.repeat_penalty,
-                        "presence_penalty": dp.presence_penalty, "frequency_penalty": dp.frequency_penalty, "dry_multiplier": dp.dry_multiplier,
-                        "dry_base": dp.dry_base, "dry_allowed_length": dp.dry_allowed_length, "dry_penalty_last_n": dp.dry_penalty_last_n,
-                        "mirostat": dp.mirostat, "mirostat_tau": dp.mirostat_tau, "mirostat_eta": dp.mirostat_eta, "n_predict": self.n_predict,
-                        "max_tokens": self.n_predict, "n_keep": 0, "ignore_eos": False, "stream": False, "n_probs": 0,
-                        "speculative.n_max": getattr(self.sched, "n_draft_default", 0)}},
+                        **self._generation_settings(Request(prompt="", n_predict=self.n_predict, sampling=dp), {}), "n_predict": self.n_predict,
+                        "max_tokens": self.n_predict}},
                     "total_slots": self.sched.n_slots, "model_alias": self.info.get("name", "model"), "model_path": self.info.get("path", self.info.get("name", "")),
                     "modalities": {"vision": False, "audio": False}, "endpoint_slots": True, "endpoint_props": False, "endpoint_metrics": True,
                     "chat_template": md.get("tokenizer.chat_template", ""), "bos_token": md.get("bos_token", ""), "eos_token": md.get("eos_token", ""),
-                    "build_info": "dlp_b200", "is_sleeping": False,
+                    "build_info": "dlp_b200", "is_sleeping": False, "webui": False, "webui_settings": {},
                     # this server's own fields
                     "model": self.info, "n_ctx": self.sched.eng.n_ctx, "uptime_s": round(time.time() - self.t_start, 1)})
                 return True
@@ -333,7 +330,7 @@ class Orchestrator:
                 return True
             if method in ("GET", "HEAD"):
                 return await self.static(path, writer, head=(method == "HEAD"))
-            await self._json(writer, {"error": "not found"}, "404 Not Found")
+            await self._json(writer, {"error": {"code": 404, "message": "File Not Found", "type": "not_found_error"}}, "404 Not Found")
             return True
         except json.JSONDecodeError as e:
             await self._json(writer, *self._bad_request(f"invalid JSON: {e}"))
@@ -351,17 +348,24 @@ class Orchestrator:
         try:
             idx = int(path.split("/")[2])
             slot = self.sched.slots[idx]
+            if idx < 0:
+                raise IndexError
         except (ValueError, IndexError):
-            await self._json(writer, {"error": "no such slot"}, "404 Not Found")
+            await self._json(writer, *self._bad_request("Invalid slot ID"))
             return True
         action = self._query.get("action", "")
+        if action not in ("save", "restore", "erase"):
+            await self._json(writer, *self._bad_request("Invalid action"))
+            return True
         if action in ("save", "restore") and not self.slot_save_path:
-            await self._json(writer, {"error": "start the server with --slot-save-path"}, "501 Not Implemented")
+            await self._json(writer, {"error": {"code": 501, "message": "This server does not support slots action. Start it with `--slot-save-path`",
+                                                "type": "not_supported_error"}}, "501 Not Implemented")
             return True
         fname = os.path.basename(str(d.get("filename", f"slot{idx}.bin")))
         fpath = os.path.join(self.slot_save_path or "", fname)
 
         def job(eng):
+            t0 = time.time()
             if slot.state.name != "IDLE":
                 raise RuntimeError("slot is busy")
             if action == "erase":
@@ -374,22 +378,27 @@ class Orchestrator:
                 if slot.sid is None:
                     raise RuntimeError("slot is empty")
                 nbytes = session.save_sequence(eng, slot.sid, fpath, slot.cache_tokens)
-                return {"id_slot": idx, "filename": fname, "n_saved": len(slot.cache_tokens), "n_written": nbytes}
+                return {"id_slot": idx, "filename": fname, "n_saved": len(slot.cache_tokens), "n_written": nbytes,
+                        "timings": {"save_ms": round((time.time() - t0) * 1e3, 3)}}
             if action == "restore":
                 if slot.sid is None:
                     slot.sid = eng.alloc_seq()
-                hdr = session.load_sequence(eng, slot.sid, fpath)
+                try:
+                    hdr = session.load_sequence(eng, slot.sid, fpath)
+                except (OSError, ValueError, KeyError) as e:
+                    raise RuntimeError(f"Unable to restore slot, no available space in KV cache or invalid slot save file ({e})")
                 slot.cache_tokens = list(hdr.get("tokens") or [])[: hdr["n_tokens"]]
                 slot.n_past = len(slot.cache_tokens)
                 if slot.n_past != hdr["n_tokens"]:          # no token ids in the file: the cache cannot be matched to prompts
                     eng.truncate_seq(slot.sid, 0)
                     slot.cache_tokens, slot.n_past = [], 0
-                return {"id_slot": idx, "filename": fname, "n_restored": slot.n_past}
-            raise ValueError("action must be save, restore or erase")
+                return {"id_slot": idx, "filename": fname, "n_restored": slot.n_past, "n_read": os.path.getsize(fpath),
+                        "timings": {"restore_ms": round((time.time() - t0) * 1e3, 3)}}
+            raise ValueError("Invalid action")
         try:
             res = await asyncio.get_running_loop().run_in_executor(None, self.sched.run_on_engine, job)
         except (RuntimeError, ValueError, OSError) as e:
-            await self._json(writer, {"error": str(e)}, "400 Bad Request")
+            await self._json(writer, *self._bad_request(str(e)))
             return True
         await self._json(writer, res)
         return True
@@ -402,7 +411,7 @@ class Orchestrator:
         if os.path.isdir(full):
             full = os.path.join(full, "index.html")
         if not (full == root or full.startswith(root + os.sep)) or not os.path.isfile(full):
-            await self._send(writer, "404 Not Found", b"", "text/plain")
+            await self._json(writer, {"error": {"code": 404, "message": "File Not Found", "type": "not_found_error"}}, "404 Not Found")
             return True
         data = open(full, "rb").read()
         ctype = mimetypes.guess_type(full)[0] or "application/octet-stream"
@@ -516,6 +525,7 @@ class Orchestrator:
                       n_probs=_as(int, d.get("n_probs"), 0) or (_as(int, d.get("logprobs"), 0) if openai else 0),
                       post_sampling_probs=bool(d.get("post_sampling_probs", False)))
         req.n_predict_asked = n_predict
+        req.want_slot = _as(int, d.get("id_slot"), -1)
         return req
 
     def _generation_settings(self, req: Request, d: dict) -> dict:
@@ -647,7 +657,7 @@ class Orchestrator:
             return True
         tools = d.get("tools") or []
         setup = toolcall.prepare(d.get("messages", []), tools, d.get("tool_choice", "auto"), bool(d.get("parallel_tool_calls", False)))
-        prompt = apply_chat_template(self.info.get("metadata", {}), setup.messages)
+        prompt = apply_chat_template(self.info.get("metadata", {}), setup.messages, bool(d.get("add_generation_prompt", True)))
         n_predict = _as(int, d.get("max_tokens", d.get("max_completion_tokens")), self.n_predict)
         n_predict = self.sched.eng.n_ctx if n_predict == -1 else max(1, n_predict)
         stop = d.get("stop") or []

@@ -219,6 +219,9 @@ class Scheduler:
         return n
 
     def _pick_slot(self, req: Request) -> Slot | None:
+        want = getattr(req, "want_slot", -1)
+        if 0 <= want < len(self.slots):       # `id_slot`: the request waits for that slot (server-context.cpp get_slot_by_id)
+            return self.slots[want] if self.slots[want].state == SlotState.IDLE else None
         idle = [s for s in self.slots if s.state == SlotState.IDLE]
         if not idle:
             return None

@@ -46,7 +46,7 @@ def pair(tmp_models, tmp_path_factory):
     env = ref_build.cpu_env(str(tmp_path_factory.mktemp("refsrv")))
     rp = _free_port()
     proc = subprocess.Popen([ref_build.exe("llama-server"), "-m", model, "-ngl", "0", "-c", "512", "-np", "2", "--host", "127.0.0.1", "--port", str(rp), "-t", "4",
-                             "--no-warmup", "--metrics", "--slots"], env=env, stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL)
+                             "--no-warmup", "--metrics", "--slots", "--slot-save-path", str(tmp_path_factory.mktemp("refslots")) + "/"], env=env, stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL)
     for _ in range(200):
         try:
             _get(rp, "/health")
@@ -58,7 +58,7 @@ def pair(tmp_models, tmp_path_factory):
         pytest.skip("the reference server did not come up here")
     sched, info, logs = build_service(model, device="cpu", n_ctx=512, n_slots=2, n_batch=64)
     sched.start()
-    orch = Orchestrator(sched, info, n_predict=16, startup_logs=logs)
+    orch = Orchestrator(sched, info, n_predict=16, startup_logs=logs, slot_save_path=str(tmp_path_factory.mktemp("ourslots")))
     op = _free_port()
     loop = asyncio.new_event_loop()
     threading.Thread(target=lambda: loop.run_until_complete(orch.serve("127.0.0.1", op)), daemon=True).start()
@@ -494,3 +494,35 @@ def test_the_remaining_routes_answer_like_the_reference(pair):
     assert a["content"] == b["content"] and a["usage"] == b["usage"] and a["stop_reason"] == b["stop_reason"]
     ma, mb = call(ours, "GET", "/models")[1]["data"][0]["meta"], call(ref, "GET", "/models")[1]["data"][0]["meta"]
     assert all(ma[k] == mb[k] for k in ("n_vocab", "n_ctx_train", "n_embd", "n_params"))
+
+
+def test_props_slot_actions_and_errors_agree(pair):
+    """`/props` key for key, slot save / restore / erase answers (counts equal: the same prompt is resident on both sides), the refusals of a bad
+    slot id / action / unknown route with the same status and error type, and `add_generation_prompt: false` on `/apply-template`."""
+    ours, ref = pair
+
+    def call(port, method, path, body=None):
+        r = urllib.request.Request(f"http://127.0.0.1:{port}{path}", json.dumps(body).encode() if body is not None else None,
+                                   {"Content-Type": "application/json"}, method=method)
+        try:
+            return 200, json.loads(urllib.request.urlopen(r, timeout=60).read())
+        except urllib.error.HTTPError as e:
+            return e.code, json.loads(e.read())
+    (sa, a), (sb, b) = call(ours, "GET", "/props"), call(ref, "GET", "/props")
+    assert sa == sb == 200 and _keys(b) - _keys(a) == set(), sorted(_keys(b) - _keys(a))
+    for port in (ours, ref):
+        assert call(port, "POST", "/completion", {"prompt": "one two three four", "n_predict": 3, "temperature": 0, "id_slot": 0})[0] == 200
+    counts = {}
+    for action, body in [("save", {"filename": "s0.bin"}), ("restore", {"filename": "s0.bin"}), ("erase", None)]:
+        (sa, a), (sb, b) = call(ours, "POST", f"/slots/0?action={action}", body), call(ref, "POST", f"/slots/0?action={action}", body)
+        assert sa == sb == 200 and _keys(b) - _keys(a) == set(), (action, a, b)
+        key = {"save": "n_saved", "restore": "n_restored", "erase": "n_erased"}[action]
+        assert a[key] == b[key] > 0, (action, a, b)
+        counts[action] = a[key]
+    assert counts["save"] == counts["restore"] == counts["erase"]
+    for method, path, body, status in [("POST", "/slots/9?action=erase", None, 400), ("POST", "/slots/0?action=bogus", None, 400), ("GET", "/nonexistent", None, 404),
+                                       ("POST", "/nonexistent", {}, 404)]:
+        (sa, a), (sb, b) = call(ours, method, path, body), call(ref, method, path, body)
+        assert sa == sb == status and a["error"]["type"] == b["error"]["type"] and a["error"]["code"] == b["error"]["code"], (path, a, b)
+    body = {"messages": [{"role": "user", "content": "u"}], "add_generation_prompt": False}
+    assert call(ours, "POST", "/apply-template", body)[1] == call(ref, "POST", "/apply-template", body)[1]
