@@ -703,6 +703,13 @@ class Orchestrator:
                             reason = "tool_calls"
                         if msg.content:
                             out += chunk({"content": msg.content}, None)
+                    usage = {"completion_tokens": len(req.output_ids), "prompt_tokens": len(req.prompt_ids),
+                             "total_tokens": len(req.prompt_ids) + len(req.output_ids)}
+                    if isinstance(d.get("stream_options"), dict) and d["stream_options"].get("include_usage"):
+                        # OpenAI `stream_options.include_usage`: the closing chunk stays bare, one more chunk without choices carries the usage
+                        tail = {"choices": [], "created": int(time.time()), "id": rid, "model": model, "system_fingerprint": FINGERPRINT,
+                                "object": "chat.completion.chunk", "usage": usage, "timings": req.timings()}
+                        return out + chunk({}, reason) + b"data: " + json.dumps(tail).encode() + b"\n\n" + b"data: [DONE]\n\n"
                     return out + chunk({}, reason, timings=req.timings()) + b"data: [DONE]\n\n"
                 return None
 
@@ -781,17 +788,20 @@ class Orchestrator:
 
             def ev(name, o):
                 return f"event: {name}\ndata: {json.dumps(o)}\n\n".encode()
-            writer.write(ev("message_start", {"type": "message_start", "message": {"id": rid, "type": "message", "role": "assistant", "model": model,
-                                                                                   "content": [], "stop_reason": None}}))
+            n_in = len(self.sched.tok.encode(req.prompt)) if isinstance(req.prompt, str) else len(req.prompt)
+            writer.write(ev("message_start", {"type": "message_start", "message": {"id": rid, "type": "message", "role": "assistant", "content": [], "model": model,
+                                                                                   "stop_reason": None, "stop_sequence": None,
+                                                                                   "usage": {"input_tokens": n_in, "output_tokens": 0}}}))
             writer.write(ev("content_block_start", {"type": "content_block_start", "index": 0, "content_block": {"type": "text", "text": ""}}))
 
             def fmt(kind, content):
                 if kind == "token":
                     return ev("content_block_delta", {"type": "content_block_delta", "index": 0, "delta": {"type": "text_delta", "text": content}})
                 if kind == "done":
-                    reason = "max_tokens" if content == "length" else "end_turn"
+                    reason = "max_tokens" if content == "length" else "stop_sequence" if req.stop_type == "word" else "end_turn"
                     return (ev("content_block_stop", {"type": "content_block_stop", "index": 0}) +
-                            ev("message_delta", {"type": "message_delta", "delta": {"stop_reason": reason}, "usage": {"output_tokens": len(req.output_ids)}}) +
+                            ev("message_delta", {"type": "message_delta", "delta": {"stop_reason": reason, "stop_sequence": req.stopping_word or None},
+                                                 "usage": {"output_tokens": len(req.output_ids)}}) +
                             ev("message_stop", {"type": "message_stop"}))
                 return None
             await self._stream_request(req, writer, fmt)
@@ -799,7 +809,8 @@ class Orchestrator:
         await self._run_blocking(req)
         await self._json(writer, {"id": rid, "type": "message", "role": "assistant", "model": model,
                                   "content": [{"type": "text", "text": req.text}],
-                                  "stop_reason": "max_tokens" if req.finish_reason == "length" else "end_turn", "stop_sequence": None,
+                                  "stop_reason": "max_tokens" if req.finish_reason == "length" else "stop_sequence" if req.stop_type == "word" else "end_turn",
+                                  "stop_sequence": req.stopping_word or None,
                                   "usage": {"input_tokens": len(req.prompt_ids), "output_tokens": len(req.output_ids)}})
         return True
 

@@ -526,3 +526,28 @@ def test_props_slot_actions_and_errors_agree(pair):
         assert sa == sb == status and a["error"]["type"] == b["error"]["type"] and a["error"]["code"] == b["error"]["code"], (path, a, b)
     body = {"messages": [{"role": "user", "content": "u"}], "add_generation_prompt": False}
     assert call(ours, "POST", "/apply-template", body)[1] == call(ref, "POST", "/apply-template", body)[1]
+
+
+def test_event_streams_agree(pair):
+    """The three streaming dialects event by event: `/v1/completions`, `/v1/chat/completions` with `stream_options.include_usage` (one more chunk
+    without choices carrying the usage) and Anthropic `/v1/messages` (event names, every key of every event, the deltas themselves)."""
+    ours, ref = pair
+    msgs = [{"role": "user", "content": "hi"}]
+
+    def events(port, path, body):
+        r = urllib.request.Request(f"http://127.0.0.1:{port}{path}", json.dumps(body).encode(), {"Content-Type": "application/json"})
+        text = urllib.request.urlopen(r, timeout=60).read().decode()
+        names = [ln[7:] for ln in text.split("\n") if ln.startswith("event: ")]
+        return names, [json.loads(ln[6:]) for ln in text.split("\n") if ln.startswith("data: {")], text.rstrip().endswith("data: [DONE]")
+    for path, body in [("/v1/completions", {"prompt": "one", "max_tokens": 2, "temperature": 0, "stream": True}),
+                       ("/v1/chat/completions", {"messages": msgs, "max_tokens": 2, "temperature": 0, "stream": True, "stream_options": {"include_usage": True}}),
+                       ("/v1/messages", {"messages": msgs, "max_tokens": 2, "temperature": 0, "stream": True})]:
+        (na, ea, da), (nb, eb, db) = events(ours, path, body), events(ref, path, body)
+        assert na == nb and len(ea) == len(eb) and da == db, (path, na, nb, len(ea), len(eb))
+        for x, y in zip(ea, eb):
+            assert _keys(y) - _keys(x) == set(), (path, sorted(_keys(y) - _keys(x)))
+            for k in ("choices", "delta", "usage", "type", "index", "content_block"):
+                if k in y and k != "usage":
+                    assert x[k] == y[k], (path, k, x[k], y[k])
+            if "usage" in y and "timings" not in y.get("usage", {}):
+                assert x["usage"] == y["usage"], (path, x["usage"], y["usage"])
