@@ -255,7 +255,12 @@ class Orchestrator:
             if method == "POST" and path in ("/v1/chat/completions", "/chat/completions"):
                 return await self.chat_completions(json.loads(body or b"{}"), writer)
             if method == "POST" and path in ("/api/generate", "/api/chat"):
-                return await self.ollama(path, json.loads(body or b"{}"), writer)
+                d = json.loads(body or b"{}")
+                # the reference registers /api/chat on its OpenAI chat handler (server.cpp: `post_chat_completions`), so a body without any of
+                # Ollama's own fields is answered in that format; one that carries `options` / `format` / `keep_alive` gets Ollama's NDJSON
+                if path == "/api/chat" and isinstance(d, dict) and not any(k in d for k in ("options", "format", "keep_alive")):
+                    return await self.chat_completions(d, writer)
+                return await self.ollama(path, d, writer)
             if method == "GET" and path == "/api/tags":
                 await self._json(writer, {"models": [{"name": self.info.get("name", "model"), "model": self.info.get("name", "model"),
                                                       "details": {"format": "gguf", "family": self.info.get("arch", "llama")}}]})

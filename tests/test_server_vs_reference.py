@@ -485,6 +485,7 @@ def test_the_remaining_routes_answer_like_the_reference(pair):
     for method, path, body in [("GET", "/v1/health", None), ("GET", "/models", None), ("GET", "/v1/models", None), ("POST", "/api/show", {"name": "x"}),
                                ("GET", "/lora-adapters", None), ("POST", "/lora-adapters", []), ("POST", "/v1/messages/count_tokens", {"messages": msgs}),
                                ("POST", "/chat/completions", {"messages": msgs, "max_tokens": 2, "temperature": 0}),
+                               ("POST", "/api/chat", {"messages": msgs, "max_tokens": 2, "temperature": 0}),
                                ("POST", "/v1/messages", {"messages": msgs, "max_tokens": 3, "temperature": 0})]:
         (sa, a), (sb, b) = call(ours, method, path, body), call(ref, method, path, body)
         assert sa == sb == 200, (path, a, b)
