@@ -156,3 +156,39 @@ def test_cvector_generator_finds_the_same_directions(tmp_path, method):
         else:
             ea, eb = float((rows[il] @ a).pow(2).sum()), float((rows[il] @ b).pow(2).sum())
             assert eb >= 0.999 * ea, (n, ea, eb)       # ours is the optimum; the reference's randomly started iteration lands at or below it
+
+
+def test_bench_output_has_the_columns_of_llama_bench(tmp_models, tmp_path):
+    """`dlp_bench.py -o json|jsonl|csv|md` against the reference's `llama-bench` on the same file: every column of the reference's records is
+    present under its name, the identifying values (file, parameter count, size on disk, test shape) are equal, the CSV header starts with
+    the reference's header, and the markdown table has its columns."""
+    import csv
+    import io
+    import json
+    from baseline import reference as ref_build
+    why = ref_build.ensure(allow_build=False)
+    if why is not None or not ref_build.have("llama-bench"):
+        pytest.skip(f"reference binaries unavailable: {why}")
+    model = tmp_models[("tiny", "F16")]
+    env = ref_build.cpu_env(str(tmp_path))
+    common = ["-m", model, "-p", "16", "-n", "4", "-r", "2"]
+
+    def ref(fmt):
+        p = subprocess.run([ref_build.exe("llama-bench"), *common, "-ngl", "0", "-t", "2", "-o", fmt], env=env, capture_output=True, text=True, timeout=300)
+        assert p.returncode == 0, p.stderr[-400:]
+        return p.stdout
+    a, b = json.loads(ours("dlp_bench.py", *common, "--device", "cpu", "-o", "json")), json.loads(ref("json"))
+    assert len(a) == len(b) == 2
+    for x, y in zip(a, b):
+        assert set(y) - set(x) == set(), sorted(set(y) - set(x))
+        for k in ("model_filename", "model_size", "model_n_params", "n_prompt", "n_gen", "n_depth", "type_k", "type_v"):
+            assert x[k] == y[k], (k, x[k], y[k])
+        assert len(x["samples_ns"]) == len(x["samples_ts"]) == 2 and x["avg_ts"] > 0 and abs(x["avg_ns"] * x["avg_ts"] / 1e9 / (x["n_prompt"] + x["n_gen"]) - 1) < 0.5
+    ha = next(csv.reader(io.StringIO(ours("dlp_bench.py", *common, "--device", "cpu", "-o", "csv"))))
+    hb = next(csv.reader(io.StringIO(ref("csv"))))
+    assert ha[:len(hb)] == hb
+    ma, mb = ours("dlp_bench.py", *common, "--device", "cpu", "-o", "md").splitlines()[0], ref("md").splitlines()[0]
+    cols = lambda line: [c.strip() for c in line.strip("|").split("|")]      # noqa: E731
+    assert set(cols(mb)) - {"threads"} <= set(cols(ma))
+    jl = [json.loads(ln) for ln in ours("dlp_bench.py", *common, "--device", "cpu", "-o", "jsonl").splitlines() if ln.startswith("{")]
+    assert [r["test"] for r in jl] == ["pp16", "tg4"]

@@ -103,7 +103,8 @@ def main(argv=None):
             ms = timed(lambda: (stage.prefill(sid, toks, chunk=a.ubatch_size) if stage else eng.prefill(sid, toks, chunk=a.ubatch_size)))
             if rep:
                 ts.append(n_p / ms * 1e3)
-        rows.append({"test": f"pp{n_p}{tag}", "n_prompt": n_p, "n_gen": 0, "n_depth": depth, "avg_ts": statistics.mean(ts), "stddev_ts": statistics.pstdev(ts)})
+        rows.append({"test": f"pp{n_p}{tag}", "n_prompt": n_p, "n_gen": 0, "n_depth": depth, "avg_ts": statistics.mean(ts), "stddev_ts": statistics.pstdev(ts),
+                     "samples_ts": ts, "n_tok": n_p})
     for depth in depths:
      tag = f" @ d{depth}" if depth else ""
      for n_g in gens:
@@ -134,31 +135,66 @@ def main(argv=None):
             if rep:
                 ts.append(n_g * B / ms * 1e3)
         rows.append({"test": f"tg{n_g}" + (f"@b{B}" if B > 1 else "") + tag, "n_prompt": 0, "n_gen": n_g, "n_depth": depth, "batch": B, "microbatches": n_mb,
-                     "avg_ts": statistics.mean(ts), "stddev_ts": statistics.pstdev(ts)})
+                     "avg_ts": statistics.mean(ts), "stddev_ts": statistics.pstdev(ts), "samples_ts": ts, "n_tok": n_g * B})
     if grid.rank == 0:
-        meta = {"model": os.path.basename(a.model), "params": cfg.n_params(), "size_bytes": w.nbytes(), "pp": grid.pp, "tp": grid.tp,
+        # every row carries llama-bench's own columns under its names (llama-bench.cpp `test::get_fields`), so that scripts written against
+        # `llama-bench -o json|jsonl|csv|sql` read these files too, plus this tool's extras (pp, tp, tp_impl, batch, microbatches, test)
+        import datetime
+        import platform
+        from distributed_llm_pipeline_b200.gguf.constants import FTYPE
+        ftype = {v: k for k, v in FTYPE.items()}.get(int(f.metadata.get("general.file_type", 1)), "?")
+        size = sum(int(t.nbytes) for t in f.tensors.values()) if all(hasattr(t, "nbytes") for t in f.tensors.values()) else os.path.getsize(a.model)
+        gpu = torch.cuda.get_device_name(grid.device) if cuda else ""
+        cpu = next((ln.split(":", 1)[1].strip() for ln in open("/proc/cpuinfo") if ln.startswith("model name")), platform.processor()) \
+            if os.path.exists("/proc/cpuinfo") else platform.processor()
+        ref_meta = {"build_commit": "dlp_b200", "build_number": 0, "cpu_info": cpu, "gpu_info": ", ".join([gpu] * grid.world) if gpu else "",
+                    "backends": "CUDA" if cuda else "CPU", "model_filename": a.model, "model_type": f"{cfg.arch} {cfg.n_params() / 1e9:.2f}B {ftype}",
+                    "model_size": size, "model_n_params": cfg.n_params(), "n_batch": a.batch_size if hasattr(a, "batch_size") else 2048, "n_ubatch": a.ubatch_size,
+                    "n_threads": torch.get_num_threads(), "cpu_mask": "0x0", "cpu_strict": False, "poll": 50, "type_k": "f16", "type_v": "f16",
+                    "n_gpu_layers": cfg.n_layer + 1 if cuda else 0, "n_cpu_moe": 0, "split_mode": "row" if grid.tp > 1 else "layer", "main_gpu": 0,
+                    "no_kv_offload": False, "flash_attn": True, "devices": "auto", "tensor_split": a.tensor_split or "0.00", "tensor_buft_overrides": "none",
+                    "use_mmap": not getattr(a, "no_mmap", False), "use_direct_io": bool(getattr(a, "direct_io", False)), "embeddings": False,
+                    "no_op_offload": 0, "no_host": False}
+        meta = {**ref_meta, "model": os.path.basename(a.model), "params": cfg.n_params(), "size_bytes": w.nbytes(), "pp": grid.pp, "tp": grid.tp,
                 "tp_impl": a.tp_impl if grid.tp > 1 else None, "backend": "dlp_b200"}
+        now = datetime.datetime.now(datetime.timezone.utc).strftime("%Y-%m-%dT%H:%M:%SZ")
+        for r in rows:
+            ns = [r["n_tok"] / t * 1e9 for t in r["samples_ts"]]
+            r.update(test_time=now, avg_ns=int(statistics.mean(ns)), stddev_ns=int(statistics.pstdev(ns)), samples_ns=[int(x) for x in ns])
+            r.pop("n_tok")
+        ref_cols = list(ref_meta) + ["n_prompt", "n_gen", "n_depth", "test_time", "avg_ns", "stddev_ns", "avg_ts", "stddev_ts"]
         if a.output == "json":
             print(json.dumps([dict(meta, **r) for r in rows], indent=1))
         elif a.output == "jsonl":
             for r in rows:
                 print(json.dumps(dict(meta, **r)))
-        elif a.output == "sql":      # same idea as llama-bench -o sql: a table definition plus one INSERT per test
-            print("CREATE TABLE IF NOT EXISTS test (model TEXT, params INTEGER, size_bytes INTEGER, pp INTEGER, tp INTEGER, tp_impl TEXT, "
-                  "backend TEXT, test TEXT, n_prompt INTEGER, n_gen INTEGER, avg_ts REAL, stddev_ts REAL);")
+        elif a.output == "sql":      # llama-bench -o sql: the table definition plus one INSERT per test, its columns first
+            cols = ref_cols + ["pp", "tp", "tp_impl", "test"]
+            kinds = {"build_number": "INTEGER", "model_size": "INTEGER", "model_n_params": "INTEGER", "n_batch": "INTEGER", "n_ubatch": "INTEGER", "n_threads": "INTEGER",
+                     "poll": "INTEGER", "n_gpu_layers": "INTEGER", "n_cpu_moe": "INTEGER", "main_gpu": "INTEGER", "no_op_offload": "INTEGER", "n_prompt": "INTEGER",
+                     "n_gen": "INTEGER", "n_depth": "INTEGER", "avg_ns": "INTEGER", "stddev_ns": "INTEGER", "avg_ts": "REAL", "stddev_ts": "REAL", "pp": "INTEGER",
+                     "tp": "INTEGER"}
+            print("CREATE TABLE IF NOT EXISTS test (\n" + ",\n".join(f"  {c} {kinds.get(c, 'TEXT')}" for c in cols) + "\n);\n")
             for r in rows:
                 d = dict(meta, **r)
-                vals = ", ".join("NULL" if d[k] is None else (f"'{d[k]}'" if isinstance(d[k], str) else f"{d[k]}")
-                                 for k in ("model", "params", "size_bytes", "pp", "tp", "tp_impl", "backend", "test", "n_prompt", "n_gen", "avg_ts", "stddev_ts"))
-                print(f"INSERT INTO test VALUES ({vals});")
+                vals = ", ".join("NULL" if d[k] is None else f"'{int(d[k]) if isinstance(d[k], bool) else d[k]}'" for k in cols)
+                print(f"INSERT INTO test ({', '.join(cols)}) VALUES ({vals});")
         elif a.output == "csv":
-            print("model,pp,tp,test,avg_ts,stddev_ts")
+            cols = ref_cols + ["pp", "tp", "test"]
+            print(",".join(cols))
             for r in rows:
-                print(f"{meta['model']},{grid.pp},{grid.tp},{r['test']},{r['avg_ts']:.2f},{r['stddev_ts']:.2f}")
-        else:
-            print("| model | size | pp x tp | test | t/s |\n|---|---:|---|---|---:|")
+                d = dict(meta, **r)
+                print(",".join('"' + (str(int(d[k])) if isinstance(d[k], bool) else f"{d[k]:.6f}" if isinstance(d[k], float) else str(d[k])) + '"' for k in cols))
+        else:       # the markdown table of llama-bench (model | size | params | backend | ngl | test | t/s) with the grid in a column of its own
+            print(f"| {'model':<30} | {'size':>10} | {'params':>10} | {'backend':<10} | {'ngl':>3} | {'pp x tp':>7} | {'test':>15} | {'t/s':>20} |")
+            print(f"| {'-' * 30} | {'-' * 9}: | {'-' * 9}: | {'-' * 10} | {'-' * 2}: | {'-' * 6}: | {'-' * 14}: | {'-' * 19}: |")
+            sz = f"{size / 2**30:.2f} GiB" if size >= 2**30 else f"{size / 2**20:.2f} MiB"
+            pr = f"{cfg.n_params() / 1e9:.2f} B" if cfg.n_params() >= 1e9 else f"{cfg.n_params() / 1e6:.2f} M"
             for r in rows:
-                print(f"| {meta['model']} | {w.nbytes() / 2**30:.2f} GiB/rank | {grid.pp} x {grid.tp} | {r['test']} | {r['avg_ts']:.2f} ± {r['stddev_ts']:.2f} |")
+                ts = f"{r['avg_ts']:.2f} ± {r['stddev_ts']:.2f}"
+                print(f"| {meta['model_type']:<30} | {sz:>10} | {pr:>10} | {meta['backends']:<10} | {meta['n_gpu_layers']:>3} | {f'{grid.pp} x {grid.tp}':>7} | "
+                      f"{r['test']:>15} | {ts:>20} |")
+            print("\nbuild: dlp_b200")
     if grid.world > 1:
         from distributed_llm_pipeline_b200.parallel.grid import shutdown
         shutdown(0)
