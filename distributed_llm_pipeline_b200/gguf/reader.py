@@ -121,6 +121,14 @@ class GGUFFile:
             vtype = ValueType(cur.take("<I"))
             self.metadata[key] = cur.value(vtype)
             self.metadata_types[key] = vtype
+        # `--override-kv KEY=TYPE:VALUE` (and the rope / YaRN flags built on it): replaces metadata values of model files for every loader in
+        # the process; only files that describe a model (they carry an architecture) and not adapters / importance matrices are touched
+        if os.environ.get("DLP_OVERRIDE_KV") and "general.architecture" in self.metadata and self.metadata.get("general.type", "model") == "model":
+            from ..utils.args import parse_override_kv
+            for spec in os.environ["DLP_OVERRIDE_KV"].split(";"):
+                if spec.strip():
+                    k, v = parse_override_kv(spec, str(self.metadata["general.architecture"]))
+                    self.metadata[k] = v
         self.alignment = int(self.metadata.get("general.alignment", GGUF_DEFAULT_ALIGNMENT))
         self.tensors: dict[str, TensorInfo] = {}
         for _ in range(n_tensors):

@@ -290,7 +290,7 @@ class Orchestrator:
                 inp = d.get("input", d.get("content", ""))
                 items = inp if isinstance(inp, list) and (not inp or not isinstance(inp[0], int)) else [inp]
                 loop = asyncio.get_running_loop()
-                pooling = str(d.get("pooling", "mean"))
+                pooling = str(d.get("pooling", self.info.get("pooling", "mean")))
                 vecs = [await loop.run_in_executor(None, self.sched.embed, it, pooling) for it in items]
                 if path.startswith("/v1"):
                     await self._json(writer, {"object": "list", "model": self.info.get("name", "model"),
@@ -1137,8 +1137,20 @@ def main(argv=None):
     ap.add_argument("--slot-save-path", default=None, help="directory for /slots/{id}?action=save|restore files")
     ap.add_argument("--context-shift", action="store_true", help="slide the context window instead of stopping at n_ctx")
     ap.add_argument("--chat-template", default=None, help="built-in chat format by name instead of the model's own template (chatml, llama3, mistral-v7, gemma, ...)")
+    ap.add_argument("-a", "--alias", default=None, help="model name reported by the API")
+    ap.add_argument("--api-key-file", default=None, help="file with one API key per line (the first is used)")
+    ap.add_argument("--chat-template-file", default=None, help="Jinja chat template read from a file (replaces the model's own)")
+    ap.add_argument("--no-context-shift", action="store_true", help="stop at a full context (the default here)")
+    ap.add_argument("-to", "--timeout", type=int, default=600, help="accepted: socket time-outs are per connection here")
+    ap.add_argument("--models-dir", default=None, help="router mode: directory of .gguf files (same as --models DIR)")
+    ap.add_argument("--pooling", default=None, choices=("none", "mean", "cls", "last", "rank"), help="default pooling of /embedding (a request may name its own)")
     add_parallel_args(ap)
-    a = ap.parse_args(argv)
+    from ..utils.args import add_compat, finish_compat
+    add_compat(ap)
+    a = finish_compat(ap, ap.parse_args(argv))
+    if a.api_key_file:
+        a.api_key = next((ln.strip() for ln in open(a.api_key_file) if ln.strip()), a.api_key)
+    a.models = a.models or a.models_dir
     maybe_reexec(a, "distributed_llm_pipeline_b200.serving.orchestrator", argv)
     if a.models:
         if os.path.isdir(a.models):
@@ -1166,6 +1178,12 @@ def main(argv=None):
         if a.chat_template not in chat_templates.names():
             ap.error(f"--chat-template: unknown name {a.chat_template!r}; built-in: {', '.join(chat_templates.names())}")
         info.setdefault("metadata", {})["dlp.chat_template_name"] = a.chat_template
+    if a.chat_template_file:
+        info.setdefault("metadata", {})["tokenizer.chat_template"] = open(a.chat_template_file).read()
+    if a.alias:
+        info["name"] = a.alias
+    if a.pooling:
+        info["pooling"] = a.pooling
     sched.start()
     orch = Orchestrator(sched, info, a.static, a.predict, logs, api_key=a.api_key, max_queue=a.max_queue, slot_save_path=a.slot_save_path)
     print(f"dlp_b200 orchestrator ready: http://localhost:{a.port}", flush=True)

@@ -74,6 +74,35 @@ def main(argv=None):
         log.info(f"load_tensors: offloaded {w.cfg.n_layer + 1}/{w.cfg.n_layer + 1} layers to GPU ({dev}), {w.nbytes() / 2**20:.1f} MiB")
     log.info(f"model loaded in {time.time() - t0:.2f} s | n_ctx {a.ctx_size} | slots {a.parallel}")
     prompt = open(a.file).read() if a.file else a.prompt
+    if a.escape and not a.no_escape and not a.file:      # -e (the reference's default): \n \t \' \" \\ in a prompt given on the command line
+        for esc, ch in (("\\n", "\n"), ("\\t", "\t"), ("\\'", "'"), ('\\"', '"'), ("\\\\", "\\")):
+            prompt = prompt.replace(esc, ch)
+    system = open(a.system_prompt_file).read() if a.system_prompt_file else a.system_prompt
+    chat_mode = bool(system) or a.conversation or a.interactive or a.interactive_first
+    if a.no_conversation:
+        a.single_turn, chat_mode = True, False
+    messages: list[dict] = [{"role": "system", "content": system}] if system else []
+    if chat_mode:       # the conversation goes through the model's chat template (llama-cli's conversation mode)
+        from distributed_llm_pipeline_b200.gguf import open_gguf as _open
+        from distributed_llm_pipeline_b200.serving.orchestrator import apply_chat_template
+        md = _open(a.model).metadata
+        chat_meta = {"tokenizer.chat_template": md.get("tokenizer.chat_template", ""), "bos_token": "", "eos_token": ""}
+        if a.interactive_first and not prompt and sys.stdin.isatty():
+            prompt = input("> ")
+        messages.append({"role": "user", "content": a.in_prefix + prompt + a.in_suffix})
+        prompt = apply_chat_template(chat_meta, messages)
+    cvecs = [(p_, 1.0) for p_ in (a.control_vector or [])] + [(p_, float(sc)) for p_, sc in (a.control_vector_scaled or [])]
+    if cvecs:
+        if len(cvecs) > 1 or not hasattr(eng, "set_control_vector"):
+            sys.exit("dlp-cli: one control vector at a time, on a single-process engine (merge several with tools/dlp_cvector.py)")
+        rng = tuple(int(x) for x in a.control_vector_layer_range) if a.control_vector_layer_range else None
+        eng.set_control_vector(cvecs[0][0], cvecs[0][1], rng)
+        log.info(f"control vector {cvecs[0][0]} x {cvecs[0][1]}" + (f" on layers {rng[0]}..{rng[1]}" if rng else ""))
+    if a.verbose_prompt:
+        ids = tok.encode(prompt)
+        log.info("prompt tokens: " + " ".join(f"{i}:{tok.tokens[i]!r}" for i in ids))
+    if a.display_prompt:
+        sys.stdout.write(prompt)
     if (a.model_draft or a.lookup) and not a.rpc and sched is None:
         # draft-and-verify generation (llama-speculative / llama-lookup): greedy, single sequence
         from distributed_llm_pipeline_b200.serving.speculative import ModelDrafter, NgramDrafter, SpecStats, generate_speculative
@@ -103,7 +132,8 @@ def main(argv=None):
 
     history, last_prompt, last_reply = "", prompt, ""
     while True:
-        req = sched.generate(prompt, n_predict=a.predict, sampling=sampling_from_args(a), ignore_eos=a.ignore_eos, on_event=on_event, n_keep=a.keep)   # (--lookup / -md take the stand-alone speculative path above)
+        req = sched.generate(prompt, n_predict=a.predict, sampling=sampling_from_args(a), ignore_eos=a.ignore_eos, on_event=on_event, n_keep=a.keep,
+                             stop=list(a.reverse_prompt or []))   # (--lookup / -md take the stand-alone speculative path above)
         sys.stdout.write("\n")
         if not history:
             history = prompt
@@ -131,9 +161,15 @@ def main(argv=None):
             except OSError as e:
                 sys.stderr.write(f"cannot read file: {e}\n")
                 continue
-        if cmd != "/regen":
+        if chat_mode:
+            if cmd == "/regen":
+                messages = messages[:-1] if messages and messages[-1]["role"] == "assistant" else messages
+            else:
+                messages += [{"role": "assistant", "content": req.text}, {"role": "user", "content": a.in_prefix + prompt + a.in_suffix}]
+            prompt = apply_chat_template(chat_meta, messages)
+        elif cmd != "/regen":
             history = history + last_reply       # multi-turn: the reply becomes part of the next prompt (prefix stays cached)
-            prompt = history + prompt
+            prompt = history + a.in_prefix + prompt + a.in_suffix
         last_prompt = prompt
     log.flush()
     if pp * tp > 1 and not a.rpc:
