@@ -283,7 +283,8 @@ class Orchestrator:
                     await self._json(writer, {"tokens": ids})
                 return True
             if method == "POST" and path == "/detokenize":
-                await self._json(writer, {"content": self.sched.tok.decode(json.loads(body or b"{}").get("tokens", []), False)})
+                # control tokens are written out by name, as the reference's /detokenize does (tokens_to_str with special = true)
+                await self._json(writer, {"content": self.sched.tok.decode_with_specials([int(t) for t in json.loads(body or b"{}").get("tokens", [])])})
                 return True
             if method == "POST" and path in ("/embedding", "/embeddings", "/v1/embeddings"):
                 d = json.loads(body or b"{}")

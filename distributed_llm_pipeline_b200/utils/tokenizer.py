@@ -253,15 +253,15 @@ class Tokenizer:
                 last = m.end()
             if last < len(text):
                 segments.append((text[last:], False))
-        first = True
+        prev_special = True        # SPM: a text fragment gets the space prefix at the start AND behind every special token (llama-vocab.cpp SPM case)
         for seg, is_special in segments:
             if is_special:
                 ids.append(self.special[seg])
             else:
-                if self.model == "llama" and first and self.add_space_prefix:
+                if self.model == "llama" and prev_special and self.add_space_prefix:
                     seg = " " + seg
                 ids.extend(self._encode_plain(seg))
-            first = False
+            prev_special = is_special
         if getattr(self, "add_eos", False) and (add_bos if add_bos is not None else True):
             ids.append(getattr(self, "sep_id", self.eos_id))          # bert: [SEP], t5: </s>
         return ids
@@ -314,7 +314,7 @@ class Tokenizer:
         """Text with control tokens written out (`<s> one two`), nothing stripped: what llama-server reports as the `prompt` it ran."""
         out = bytearray()
         for i in ids:
-            if 0 <= i < self.n_vocab and self.types[i] in (TokenType.CONTROL, TokenType.USER_DEFINED):
+            if 0 <= i < self.n_vocab and self.types[i] == TokenType.CONTROL:
                 out += self.tokens[i].encode("utf-8")
             else:
                 out += self.token_bytes(i)

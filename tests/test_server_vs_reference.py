@@ -74,7 +74,8 @@ def pair(tmp_models, tmp_path_factory):
     proc.wait()
 
 
-TEXTS = ["hello there world", "The quick brown fox jumps over 13 lazy dogs!", "  leading spaces and\nnew lines\n", "ünïcödé 你好 🙂", ""]
+TEXTS = ["hello there world", "The quick brown fox jumps over 13 lazy dogs!", "  leading spaces and\nnew lines\n", "ünïcödé 你好 🙂", "",
+         "a <s> b</s>c <s>", "<s>x"]          # special tokens inside the text: the SPM space prefix returns behind each of them
 
 
 def test_tokenize_and_detokenize_agree(pair):

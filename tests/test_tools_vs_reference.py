@@ -192,3 +192,17 @@ def test_bench_output_has_the_columns_of_llama_bench(tmp_models, tmp_path):
     assert set(cols(mb)) - {"threads"} <= set(cols(ma))
     jl = [json.loads(ln) for ln in ours("dlp_bench.py", *common, "--device", "cpu", "-o", "jsonl").splitlines() if ln.startswith("{")]
     assert [r["test"] for r in jl] == ["pp16", "tg4"]
+
+
+@pytest.mark.parametrize("args", [[], ["--ids"], ["--show-count", "--no-bos"], ["--no-parse-special"]])
+def test_tokenize_tool_prints_what_llama_tokenize_prints(tmp_models, args):
+    """`dlp_tokenize.py` and `llama-tokenize` on the same file: byte-identical stdout (ids, pieces - a lone byte token as that byte, control
+    tokens by name -, escapes in the prompt, the count line), with special tokens in the middle of the text."""
+    model = tmp_models[("tiny", "F16")]
+    prompt = "hello wörld\\nx <s> y</s> z"
+    ref = subprocess.run([tool("llama-tokenize"), "-m", model, "-p", prompt, "--log-disable", *args], capture_output=True, timeout=120)
+    assert ref.returncode == 0, ref.stderr[-300:]
+    mine = subprocess.run([sys.executable, os.path.join(ROOT, "tools", "dlp_tokenize.py"), "-m", model, "-p", prompt, *args], capture_output=True, timeout=120,
+                          env=dict(os.environ, CUDA_VISIBLE_DEVICES=""))
+    assert mine.returncode == 0, mine.stderr[-300:]
+    assert mine.stdout == ref.stdout

@@ -14,16 +14,31 @@ def main(argv=None):
     ap.add_argument("-p", "--prompt", default=None)
     ap.add_argument("-f", "--file", default=None)
     ap.add_argument("--ids", action="store_true", help="print only the ids as a Python list")
-    ap.add_argument("--no-bos", action="store_true")
+    ap.add_argument("--no-bos", action="store_true", help="do not add BOS even where the model uses one")
+    ap.add_argument("--stdin", action="store_true", help="read the prompt from standard input")
+    ap.add_argument("--no-parse-special", action="store_true", help="treat special-token text in the prompt as plain text")
+    ap.add_argument("--no-escape", action="store_true", help="leave \\n, \\t ... in the prompt as they are")
+    ap.add_argument("--show-count", action="store_true", help="print the number of tokens at the end")
+    ap.add_argument("--log-disable", action="store_true", help="accepted: nothing but the tokens is written to stdout anyway")
     a = ap.parse_args(argv)
-    text = open(a.file).read() if a.file else (a.prompt or sys.stdin.read())
+    text = open(a.file).read() if a.file else (sys.stdin.read() if a.stdin or a.prompt is None else a.prompt)
+    if not a.no_escape and not a.file and not a.stdin:
+        for esc, ch in (("\\n", "\n"), ("\\t", "\t"), ("\\'", "'"), ('\\"', '"'), ("\\\\", "\\")):
+            text = text.replace(esc, ch)
     tok = Tokenizer.from_gguf(a.model)
-    ids = tok.encode(text, add_bos=not a.no_bos)
+    if a.no_parse_special:
+        saved, tok.special = tok.special, {}
+    ids = tok.encode(text, add_bos=(tok.add_bos and not a.no_bos))
+    if a.no_parse_special:
+        tok.special = saved
     if a.ids:
-        print(ids)
+        print("[" + ", ".join(str(i) for i in ids) + "]")
     else:
-        for i in ids:
-            print(f"{i:6d} -> {tok.token_bytes(i).decode('utf-8', errors='replace')!r}")
+        for i in ids:       # control tokens by name, other tokens as the text they stand for (llama-tokenize: token_to_piece with special = true)
+            piece = tok.tokens[i].encode("utf-8") if tok.types[i] in (3, 4) else tok.token_bytes(i)      # a lone byte token is written as that byte
+            sys.stdout.flush()
+            sys.stdout.buffer.write(f"{i:6d} -> '".encode() + piece + b"'\n")
+    if a.show_count:
         print(f"Total number of tokens: {len(ids)}")
 
 
