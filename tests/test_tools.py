@@ -307,3 +307,10 @@ def test_perplexity_tool_matches_llama_perplexity(tmp_models, tmp_path):
     out = _run("dlp_perplexity.py", "-m", model, "-f", str(text), "-c", "64", "--chunks", "3", "--device", "cpu")
     mine = float(re.search(r"Final estimate: PPL = ([0-9.]+)", out).group(1))
     assert abs(mine - ref_ppl) / ref_ppl < 0.02, (mine, ref_ppl)
+    # the same running line ("[1]ppl,[2]ppl,...") and the same error estimate behind "+/-"
+    ref_err = float(re.search(r"Final estimate: PPL = [0-9.]+ \+/- ([0-9.]+)", p.stdout + p.stderr).group(1))
+    my_err = float(re.search(r"Final estimate: PPL = [0-9.]+ \+/- ([0-9.]+)", out).group(1))
+    assert abs(my_err - ref_err) / ref_err < 0.05, (my_err, ref_err)
+    run_ref, run_mine = re.findall(r"\[(\d+)\]([0-9.]+),", p.stdout), re.findall(r"\[(\d+)\]([0-9.]+),", out)
+    assert [i for i, _ in run_ref] == [i for i, _ in run_mine] == ["1", "2", "3"]
+    assert all(abs(float(a) - float(b)) / float(b) < 0.02 for (_, a), (_, b) in zip(run_mine, run_ref))

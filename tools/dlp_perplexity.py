@@ -34,7 +34,7 @@ def main(argv=None):
     else:
         g = torch.Generator().manual_seed(0)
         ids = torch.randint(3, w.cfg.vocab_size, (a.ctx_size * a.chunks,), generator=g).tolist()
-    nll, count = 0.0, 0
+    nll, nll2, count = 0.0, 0.0, 0
     n_chunks = min(a.chunks, len(ids) // a.ctx_size)
     tok = Tokenizer(f.metadata)
     half = a.ctx_size // 2
@@ -48,11 +48,18 @@ def main(argv=None):
         # positions n_ctx/2 .. n_ctx-2 predict tokens n_ctx/2+1 .. n_ctx-1: the second half of the window, scored with at least half a
         # window of context (perplexity.cpp:595-640 `first = n_ctx/2`)
         tgt = torch.tensor(chunk[half + 1:], device=lp.device)
-        nll -= float(lp[half:a.ctx_size - 1].gather(1, tgt[:, None]).sum())
+        tok_nll = -lp[half:a.ctx_size - 1].gather(1, tgt[:, None]).double()
+        nll += float(tok_nll.sum())
+        nll2 += float((tok_nll * tok_nll).sum())
         count += a.ctx_size - 1 - half
         eng.free_seq(sid)
-        print(f"[{c + 1}/{n_chunks}] running PPL = {math.exp(nll / count):.4f}", flush=True)
-    print(f"Final estimate: PPL = {math.exp(nll / max(1, count)):.4f} over {count} tokens")
+        print(f"[{c + 1}]{math.exp(nll / count):.4f},", end="", flush=True)          # the reference's running line: [1]647.7593,[2]561.2521,
+    print()
+    # the reference's closing line, with its error estimate: standard error of the mean token NLL, carried over to the perplexity
+    mean = nll / max(1, count)
+    var = nll2 / max(1, count) - mean * mean
+    err = math.sqrt(var / (count - 1)) * math.exp(mean) if var > 0 and count > 1 else 0.0
+    print(f"Final estimate: PPL = {math.exp(mean):.4f} +/- {err:.5f}")
 
 
 if __name__ == "__main__":
