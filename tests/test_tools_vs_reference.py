@@ -206,3 +206,20 @@ def test_tokenize_tool_prints_what_llama_tokenize_prints(tmp_models, args):
                           env=dict(os.environ, CUDA_VISIBLE_DEVICES=""))
     assert mine.returncode == 0, mine.stderr[-300:]
     assert mine.stdout == ref.stdout
+
+
+def test_quantizer_switches_select_the_same_tensor_types(tmp_models, tmp_path):
+    """`--pure`, `--token-embedding-type`, `--output-tensor-type`, `--leave-output-tensor`, `--tensor-type PATTERN=TYPE`, lower-case / numeric type
+    names and the optional thread count: the same command line gives the same per-tensor types as `llama-quantize`."""
+    src = tmp_models[("tiny", "F16")]
+    for k, flags in enumerate([["--pure"], ["--token-embedding-type", "q8_0", "--output-tensor-type", "q5_k"], ["--leave-output-tensor"],
+                               ["--tensor-type", "attn_v=q6_k", "--tensor-type", "ffn_down=q5_k"]]):
+        ref_out, our_out = str(tmp_path / f"ref{k}.gguf"), str(tmp_path / f"ours{k}.gguf")
+        run([tool("llama-quantize"), *flags, src, ref_out, "q4_k_m", "2"])
+        ours("dlp_quantize.py", *flags, src, our_out, "q4_k_m", "2", "--fast")
+        r, o = open_gguf(ref_out), open_gguf(our_out)
+        assert {n: GGMLType(t.ggml_type).name for n, t in r.tensors.items()} == {n: GGMLType(t.ggml_type).name for n, t in o.tensors.items()}, flags
+    ours("dlp_quantize.py", src, str(tmp_path / "n.gguf"), "15", "--fast")          # llama_ftype number of Q4_K_M
+    assert open_gguf(str(tmp_path / "n.gguf")).metadata["general.file_type"] == 15
+    out = ours("dlp_quantize.py", "--dry-run", src, "q8_0")
+    assert "nothing written" in out and "blk.0.attn_q.weight" in out
