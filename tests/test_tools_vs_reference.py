@@ -223,3 +223,17 @@ def test_quantizer_switches_select_the_same_tensor_types(tmp_models, tmp_path):
     assert open_gguf(str(tmp_path / "n.gguf")).metadata["general.file_type"] == 15
     out = ours("dlp_quantize.py", "--dry-run", src, "q8_0")
     assert "nothing written" in out and "blk.0.attn_q.weight" in out
+
+
+def test_split_by_size_with_an_empty_first_shard_is_merged_by_the_reference(tmp_models, tmp_path):
+    """`--split-max-size` + `--no-tensor-first-split` (shards cut by bytes, the first one metadata only) and `--dry-run`: the reference's
+    `llama-gguf-split --merge` reassembles the set bit for bit."""
+    src = tmp_models[("tiny", "F16")]
+    plan = ours("dlp_gguf_split.py", "--split", "--split-max-size", "1M", "--no-tensor-first-split", "--dry-run", src, str(tmp_path / "dry"))
+    assert "split 00001: n_tensors = 0" in plan and not list(tmp_path.glob("dry*"))
+    shards = ours("dlp_gguf_split.py", "--split", "--split-max-size", "1M", "--no-tensor-first-split", src, str(tmp_path / "sh")).split()
+    assert len(shards) >= 3 and len(open_gguf(shards[0]).files[0].tensors) == 0
+    merged = str(tmp_path / "merged.gguf")
+    run([tool("llama-gguf-split"), "--merge", shards[0], merged])
+    a, b = open_gguf(src), open_gguf(merged)
+    assert set(a.tensors) == set(b.tensors) and all(np.array_equal(a.raw(n), b.raw(n)) for n in a.tensors)

@@ -25,13 +25,33 @@ def _copy_meta(f, w, skip_split=True):
             w.add(key, val, f.files[0].metadata_types[key])
 
 
-def split(src, prefix, max_tensors):
+def plan(f, max_tensors=0, max_bytes=0, no_tensor_first_split=False):
+    """Tensor names per shard: at most `max_tensors` tensors, or at most `max_bytes` of tensor data (a tensor larger than that gets a shard of
+    its own); with `no_tensor_first_split` the first shard carries the metadata only (gguf-split.cpp split_strategy)."""
+    groups, cur, size = [], [], 0
+    for n, t in f.tensors.items():
+        full = (max_bytes and cur and size + t.nbytes > max_bytes) or (not max_bytes and len(cur) >= max(1, max_tensors))
+        if full:
+            groups.append(cur)
+            cur, size = [], 0
+        cur.append(n)
+        size += t.nbytes
+    if cur:
+        groups.append(cur)
+    return ([[]] if no_tensor_first_split else []) + groups
+
+
+def split(src, prefix, max_tensors=128, max_bytes=0, no_tensor_first_split=False, dry_run=False):
     f = open_gguf(src)
     names = list(f.tensors)
-    groups = [names[i:i + max_tensors] for i in range(0, len(names), max_tensors)]
+    groups = plan(f, max_tensors, max_bytes, no_tensor_first_split)
     out = []
     for i, grp in enumerate(groups, 1):
         path = f"{prefix}-{i:05d}-of-{len(groups):05d}.gguf"
+        out.append(path)
+        if dry_run:
+            print(f"split {i:05d}: n_tensors = {len(grp)}, total_size = {sum(f.tensors[n].nbytes for n in grp) // 1000000}M")
+            continue
         w = GGUFWriter(path)
         if i == 1:
             _copy_meta(f, w)
@@ -44,7 +64,6 @@ def split(src, prefix, max_tensors):
             t = f.tensors[n]
             w.add_tensor(n, t.shape, t.ggml_type, lambda n=n: np.ascontiguousarray(f.raw(n)).reshape(-1))
         w.write()
-        out.append(path)
     return out
 
 
@@ -60,16 +79,26 @@ def merge(first_shard, dst):
 
 def main(argv=None):
     ap = argparse.ArgumentParser(description=__doc__.splitlines()[0])
-    ap.add_argument("--split", action="store_true")
+    ap.add_argument("--split", action="store_true", help="split (the default)")
     ap.add_argument("--merge", action="store_true")
-    ap.add_argument("--split-max-tensors", type=int, default=128)
+    ap.add_argument("--split-max-tensors", type=int, default=128, help="tensors per shard")
+    ap.add_argument("--split-max-size", default=None, metavar="N(M|G)", help="tensor bytes per shard, e.g. 500M or 2G (overrides --split-max-tensors)")
+    ap.add_argument("--no-tensor-first-split", action="store_true", help="the first shard holds the metadata only")
+    ap.add_argument("--dry-run", action="store_true", help="print the plan, write nothing")
     ap.add_argument("src")
     ap.add_argument("dst")
     a = ap.parse_args(argv)
     if a.merge:
         print(merge(a.src, a.dst))
-    else:
-        for p in split(a.src, a.dst, a.split_max_tensors):
+        return
+    max_bytes = 0
+    if a.split_max_size:
+        unit = {"M": 1000 ** 2, "G": 1000 ** 3}.get(a.split_max_size[-1].upper())
+        if unit is None or not a.split_max_size[:-1].isdigit():
+            ap.error("--split-max-size takes a number followed by M or G")
+        max_bytes = int(a.split_max_size[:-1]) * unit
+    for p in split(a.src, a.dst, a.split_max_tensors, max_bytes, a.no_tensor_first_split, a.dry_run):
+        if not a.dry_run:
             print(p)
 
 
