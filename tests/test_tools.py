@@ -314,3 +314,24 @@ def test_perplexity_tool_matches_llama_perplexity(tmp_models, tmp_path):
     run_ref, run_mine = re.findall(r"\[(\d+)\]([0-9.]+),", p.stdout), re.findall(r"\[(\d+)\]([0-9.]+),", out)
     assert [i for i, _ in run_ref] == [i for i, _ in run_mine] == ["1", "2", "3"]
     assert all(abs(float(a) - float(b)) / float(b) < 0.02 for (_, a), (_, b) in zip(run_mine, run_ref))
+
+
+def test_imatrix_files_combine_by_addition(tmp_models, tmp_path):
+    """`dlp_imatrix.py --chunk N` (start further into the text) and `--in-file a --in-file b` (combine): two halves of a text measured apart and
+    merged equal one run over the whole text; `--show-statistics` prints one line per matrix."""
+    model = tmp_models[("tiny", "F16")]
+    rnd = np.random.default_rng(3)
+    words = ["alpha", "beta", "gamma", "delta", "the", "of", "and", "to", "in", "is"]
+    text = tmp_path / "t.txt"
+    text.write_text(" ".join(words[i] for i in rnd.integers(0, len(words), 1500)))
+    a, b, ab, whole = (str(tmp_path / n) for n in ("a.gguf", "b.gguf", "ab.gguf", "whole.gguf"))
+    _run("dlp_imatrix.py", "-m", model, "-f", str(text), "-c", "64", "--chunks", "2", "-o", a)
+    _run("dlp_imatrix.py", "-m", model, "-f", str(text), "-c", "64", "--chunks", "2", "--chunk", "2", "-o", b)
+    _run("dlp_imatrix.py", "-m", model, "--in-file", a, "--in-file", b, "-o", ab)
+    _run("dlp_imatrix.py", "-m", model, "-f", str(text), "-c", "64", "--chunks", "4", "-o", whole)
+    fa, fw = open_gguf(ab), open_gguf(whole)
+    assert fa.metadata["imatrix.chunk_count"] == fw.metadata["imatrix.chunk_count"] == 4 and set(fa.names()) == set(fw.names())
+    for n in fw.names():
+        assert np.allclose(fa.array(n), fw.array(n), rtol=1e-5, atol=1e-6), n
+    out = _run("dlp_imatrix.py", "-m", model, "--in-file", whole, "--show-statistics")
+    assert "blk.0.attn_q.weight" in out and "entropy" in out

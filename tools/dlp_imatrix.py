@@ -101,17 +101,61 @@ def main(argv=None):
     ap.add_argument("-c", "--ctx-size", type=int, default=128)
     ap.add_argument("--chunks", type=int, default=-1)
     ap.add_argument("--process-output", action="store_true", help="also collect statistics for output.weight")
+    # llama-imatrix's other switches (tools/imatrix/imatrix.cpp usage)
+    ap.add_argument("--chunk", "--from-chunk", type=int, default=0, dest="from_chunk", help="skip this many chunks of the text first")
+    ap.add_argument("--in-file", action="append", default=[], help="existing imatrix GGUF to start from / to combine (may be repeated; without -f: just merge them)")
+    ap.add_argument("--parse-special", action="store_true", help="special-token text in the calibration file stands for the tokens")
+    ap.add_argument("--show-statistics", action="store_true", help="print per-matrix statistics of an imatrix (with --in-file) and exit")
+    ap.add_argument("--no-ppl", action="store_true", help="accepted: no perplexity is computed along the way here")
+    ap.add_argument("--output-frequency", type=int, default=10, help="accepted: the file is written once at the end")
+    ap.add_argument("--save-frequency", type=int, default=0, help="accepted: no intermediate snapshots")
+    ap.add_argument("--output-format", default="gguf", choices=("gguf",), help="only the GGUF layout is written (the legacy .dat layout is not)")
     a = ap.parse_args(argv)
     from distributed_llm_pipeline_b200.utils.tokenizer import Tokenizer
+
+    def raw_sums(path):      # {name: (in_sum2, counts)}, chunk count
+        fi = open_gguf(path)
+        if fi.metadata.get("general.type") != "imatrix":
+            raise SystemExit(f"{path} is not an imatrix file")
+        return ({n[:-len(".in_sum2")]: (np.array(fi.array(n), np.float64), np.array(fi.array(n[:-len(".in_sum2")] + ".counts"), np.float64))
+                 for n in fi.names() if n.endswith(".in_sum2")}, int(fi.metadata.get("imatrix.chunk_count", 0)), int(fi.metadata.get("imatrix.chunk_size", a.ctx_size)))
+    if a.show_statistics:
+        if not a.in_file:
+            ap.error("--show-statistics needs --in-file")
+        sums, _, _ = raw_sums(a.in_file[0])
+        print(f"{'tensor':48s} {'sum(act^2)':>14s} {'min':>12s} {'max':>12s} {'mean':>12s} {'std':>12s} {'entropy':>9s}")
+        for name in sorted(sums):
+            s2, cn = sums[name]
+            v = (s2 / np.maximum(cn, 1)).reshape(-1)
+            pr = v / v.sum() if v.sum() > 0 else np.full_like(v, 1.0 / v.size)
+            ent = float(-(pr[pr > 0] * np.log2(pr[pr > 0])).sum())
+            print(f"{name:48s} {v.sum():14.4f} {v.min():12.6f} {v.max():12.6f} {v.mean():12.6f} {v.std():12.6f} {ent:9.4f}")
+        return
     f = open_gguf(a.model)
-    if a.file:
-        ids = Tokenizer(f.metadata).encode(open(a.file, encoding="utf-8").read())
-    else:
-        g = torch.Generator().manual_seed(0)
-        ids = torch.randint(3, len(f.metadata["tokenizer.ggml.tokens"]), (a.ctx_size * max(1, a.chunks if a.chunks > 0 else 4),), generator=g).tolist()
-    col, n = collect(a.model, ids, a.ctx_size, a.chunks, process_output=a.process_output)
-    save(a.output, col, n, a.ctx_size, a.file or "synthetic")
-    print(f"{a.output}: {len(col.sum2)} matrices, {n} chunks of {a.ctx_size} tokens")
+    col = None
+    n, n_ctx = 0, a.ctx_size
+    if a.file or not a.in_file:
+        if a.file:
+            ids = Tokenizer(f.metadata).encode(open(a.file, encoding="utf-8").read(), parse_special=a.parse_special)
+        else:
+            g = torch.Generator().manual_seed(0)
+            ids = torch.randint(3, len(f.metadata["tokenizer.ggml.tokens"]), (a.ctx_size * (a.from_chunk + max(1, a.chunks if a.chunks > 0 else 4)),), generator=g).tolist()
+        ids = ids[a.from_chunk * a.ctx_size:]
+        col, n = collect(a.model, ids, a.ctx_size, a.chunks, process_output=a.process_output)
+    for path in a.in_file:          # statistics are sums: files combine by adding them (imatrix.cpp load_imatrix)
+        sums, chunks, n_ctx = raw_sums(path)
+        if col is None:
+            col = Collector.__new__(Collector)
+            col.sum2, col.counts = {}, {}
+        for name, (s2, cn) in sums.items():
+            if name in col.sum2 and col.sum2[name].shape == s2.shape:
+                col.sum2[name] = col.sum2[name] + s2
+                col.counts[name] = col.counts[name] + cn.reshape(col.counts[name].shape)
+            else:
+                col.sum2[name], col.counts[name] = s2.copy(), cn.copy()
+        n += chunks
+    save(a.output, col, n, n_ctx, a.file or ("synthetic" if not a.in_file else ",".join(a.in_file)))
+    print(f"{a.output}: {len(col.sum2)} matrices, {n} chunks of {n_ctx} tokens")
 
 
 if __name__ == "__main__":
