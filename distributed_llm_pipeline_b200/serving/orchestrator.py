@@ -294,8 +294,9 @@ class Orchestrator:
                 pooling = str(d.get("pooling", self.info.get("pooling", "mean")))
                 vecs = [await loop.run_in_executor(None, self.sched.embed, it, pooling) for it in items]
                 if path.startswith("/v1"):
-                    await self._json(writer, {"object": "list", "model": self.info.get("name", "model"),
-                                              "data": [{"object": "embedding", "index": i, "embedding": v} for i, v in enumerate(vecs)]})
+                    n_tok = sum(len(self.sched.tok.encode(it)) if isinstance(it, str) else len(it) for it in items)
+                    await self._json(writer, {"model": self.info.get("name", "model"), "object": "list", "usage": {"prompt_tokens": n_tok, "total_tokens": n_tok},
+                                              "data": [{"embedding": v, "index": i, "object": "embedding"} for i, v in enumerate(vecs)]})
                 else:
                     await self._json(writer, [{"index": i, "embedding": v} for i, v in enumerate(vecs)] if isinstance(inp, list) and items is inp
                                      else {"embedding": vecs[0]})

@@ -184,6 +184,16 @@ def test_embeddings_agree_with_reference_server(pair, tmp_models, tmp_path, pool
             assert len(rv) == len(ov)
             dot = sum(a * b for a, b in zip(rv, ov))
             assert dot > 0.9999 and abs(sum(a * a for a in ov) - 1.0) < 1e-3, (pooling, text, dot)
+        # the OpenAI route: the same keys (usage included), one entry per input, the same vectors
+        body = {"input": ["hello there world", "second text"], "pooling": pooling}
+        a, b = _post(ours, "/v1/embeddings", body), _post(port, "/v1/embeddings", {"input": body["input"]})
+        assert _keys(b) - _keys(a) == set(), sorted(_keys(b) - _keys(a))
+        assert a["usage"] == b["usage"] and [e["index"] for e in a["data"]] == [e["index"] for e in b["data"]] == [0, 1]
+        for x, y in zip(a["data"], b["data"]):
+            assert sum(p_ * q for p_, q in zip(x["embedding"], y["embedding"])) > 0.9999
+        # the native route with several inputs, and a rerank request (this server scores by embedding similarity: the shape is what is compared)
+        ra, rb = _post(ours, "/embedding", {"content": ["a b", "c d"], "pooling": pooling}), _post(port, "/embedding", {"content": ["a b", "c d"]})
+        assert isinstance(ra, list) and isinstance(rb, list) and len(ra) == len(rb) == 2 and [e["index"] for e in ra] == [e["index"] for e in rb]
     finally:
         p.terminate()
         p.wait()
