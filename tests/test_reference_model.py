@@ -224,3 +224,38 @@ def test_export_lora_and_control_vector(tmp_models, tmp_path):
         if il == 1:
             h = h + 2.0 * torch.from_numpy(d1)
     assert nmse(ref.head(h)[-1], got.float().flatten()) < 1e-5
+
+
+def test_engines_sharing_one_set_of_weights_run_from_several_threads(tmp_models):
+    """Counterpart of the reference's test-thread-safety.cpp (several contexts over one model, several threads): three engines built on the same
+    loaded weights generate from different prompts at the same time and give what each gives alone."""
+    import threading
+    from distributed_llm_pipeline_b200.models.llama import LlamaEngine
+    from distributed_llm_pipeline_b200.models.weights import load_weights
+    w = load_weights(tmp_models[("tiny", "Q8_0")], "cpu")
+    prompts = [[1, 5, 9, 200, 33], [1, 7, 8, 100, 42, 17, 3], [1, 250, 77, 12]]
+
+    def generate(eng, prompt, n=6):
+        sid = eng.alloc_seq()
+        out = [int(eng.prefill(sid, prompt).argmax())]
+        for _ in range(n - 1):
+            out.append(int(eng.decode([sid], [out[-1]], sample=False)[0].argmax()))
+        eng.free_seq(sid)
+        return out
+    alone = [generate(LlamaEngine(w, n_ctx=64, max_seqs=1, page_size=16, max_batch_tokens=16), p) for p in prompts]
+    engines = [LlamaEngine(w, n_ctx=64, max_seqs=1, page_size=16, max_batch_tokens=16) for _ in prompts]
+    together: list = [None] * len(prompts)
+    errors: list = []
+
+    def work(i):
+        try:
+            for _ in range(3):
+                together[i] = generate(engines[i], prompts[i])
+        except Exception as e:      # noqa: BLE001 - reported below
+            errors.append(e)
+    threads = [threading.Thread(target=work, args=(i,)) for i in range(len(prompts))]
+    for t in threads:
+        t.start()
+    for t in threads:
+        t.join(120)
+    assert not errors and together == alone
