@@ -142,9 +142,15 @@ def write_lora_gguf(path: str, deltas: dict[str, tuple[np.ndarray, np.ndarray]],
     return w.write()
 
 
+class LoadCancelled(RuntimeError):
+    """Raised by `load_weights` when its progress callback returns False."""
+
+
 def load_weights(src: str | GGUFModelFiles, device, layer_range: range | None = None, tp_rank: int = 0, tp_size: int = 1,
                  first_stage: bool = True, last_stage: bool = True, shard_vocab: bool = True,
-                 lora: list[LoraAdapter] | None = None) -> ModelWeights:
+                 lora: list[LoraAdapter] | None = None, progress=None) -> ModelWeights:
+    """`progress(fraction) -> bool` is called before every layer and once at the end (1.0); returning False abandons the load with
+    `LoadCancelled` (`llama_model_params.progress_callback`, the reference's test-model-load-cancel.cpp)."""
     f = open_gguf(src) if isinstance(src, str) else src
     lora = lora or []
     cfg = config_from_gguf(f.metadata, f.tensors)
@@ -214,6 +220,8 @@ def load_weights(src: str | GGUFModelFiles, device, layer_range: range | None = 
 
     layers: dict[int, LayerWeights] = {}
     for il in layer_range:
+        if progress is not None and progress((il - layer_range.start) / max(1, len(layer_range))) is False:
+            raise LoadCancelled(f"load of {getattr(f, 'path', 'model')} cancelled at layer {il}")
         p = f"blk.{il}."
         qr = (hq0 * D, hq1 * D)
         kr = (kv_rank * n_kv_local * D, (kv_rank + 1) * n_kv_local * D)
@@ -336,6 +344,8 @@ def load_weights(src: str | GGUFModelFiles, device, layer_range: range | None = 
             v0, v1 = _split(cfg.vocab_size, tp_size, tp_rank)
         lm = mat(name, rows=(v0, v1))
     freqs = f32("rope_freqs.weight") if "rope_freqs.weight" in f else None
+    if progress is not None and progress(1.0) is False:
+        raise LoadCancelled("load cancelled")
     return ModelWeights(cfg, layers, layer_range, tp_rank, tp_size, tok, out_norm, lm, (v0, v1), freqs,
                         n_head_local=hq1 - hq0, n_head_kv_local=n_kv_local, n_ff_local=cfg.n_ff // tp_size, out_norm_b=out_norm_b,
                         pos_embd=f32("position_embd.weight") if (cfg.learned_pos and first_stage) else None,

@@ -259,3 +259,13 @@ def test_engines_sharing_one_set_of_weights_run_from_several_threads(tmp_models)
     for t in threads:
         t.join(120)
     assert not errors and together == alone
+
+
+def test_model_load_reports_progress_and_can_be_cancelled(tmp_models):
+    """`load_weights(progress=...)`: fractions rise to 1.0; a callback that returns False abandons the load (test-model-load-cancel.cpp)."""
+    from distributed_llm_pipeline_b200.models.weights import LoadCancelled, load_weights
+    seen = []
+    w = load_weights(tmp_models[("tiny", "F16")], "cpu", progress=lambda fr: seen.append(fr) or True)
+    assert seen == sorted(seen) and seen[0] == 0.0 and seen[-1] == 1.0 and len(seen) == w.cfg.n_layer + 1
+    with pytest.raises(LoadCancelled):
+        load_weights(tmp_models[("tiny", "F16")], "cpu", progress=lambda fr: fr < 0.4)
