@@ -158,6 +158,8 @@ def _tensor_plan(cfg: ModelConfig, rope_freqs: bool):
             plan += [(p + "attn_q_norm.weight", (cfg.head_dim,), il, 0.0), (p + "attn_k_norm.weight", (cfg.head_dim,), il, 0.0)]
         if cfg.qk_norm_full:
             plan += [(p + "attn_q_norm.weight", (cfg.q_dim,), il, 0.0), (p + "attn_k_norm.weight", (cfg.kv_dim,), il, 0.0)]
+        if cfg.sub_norm:
+            plan.append((p + "attn_sub_norm.weight", (cfg.q_dim,), il, 0.0))
         plan.append((p + "attn_output.weight", (E, cfg.q_dim), il, 0.02))
         if all_bias or cfg.attn_out_bias:
             plan.append((p + "attn_output.bias", (E,), il, 0.05))
@@ -196,6 +198,8 @@ def _tensor_plan(cfg: ModelConfig, rope_freqs: bool):
                 (p + "ffn_down.weight", (E, F), il, 0.02),
                 (p + "ffn_up.weight", (F, E), il, 0.02),
             ]
+            if cfg.sub_norm:
+                plan.append((p + "ffn_sub_norm.weight", (F,), il, 0.0))
         if cfg.post_norm:
             plan.append((p + "post_ffw_norm.weight", (E,), il, 0.0))
     plan += norm("output_norm", -1, nl["out"])

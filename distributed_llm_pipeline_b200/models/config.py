@@ -59,6 +59,7 @@ class ModelConfig:
     expert_weights_scale: float = 1.0      # read and written back; applied only with moe_scale_w (the deepseek-v1 / bailingmoe builders pass scale_w = false)
     # glm4moe (GLM-4.5), dots1: DeepSeek-V3 style routing - sigmoid scores, a per-expert bias added for the SELECTION only, weights = the
     # unbiased scores of the selected experts (renormalised when the file says so) times expert_weights_scale (llama-graph.cpp:1037-1143)
+    sub_norm: bool = False         # bitnet: one more RMSNorm in front of the attention output matrix and of the MLP's down matrix
     moe_gating: str = "softmax"    # "softmax" | "sigmoid"
     moe_sel_bias: bool = False     # `blk.N.exp_probs_b.bias`
     moe_scale_w: bool = False
@@ -80,7 +81,7 @@ class ModelConfig:
     def generic(self) -> bool:
         """True for families that run the unfused layer path (models/llama.py `_layer_generic`)."""
         return (self.norm_type != "rms" or self.ffn_act != "swiglu" or self.parallel_residual or self.post_norm or not self.pre_norm or self.attn_out_bias
-                or self.qk_norm_full)
+                or self.qk_norm_full or self.sub_norm)
 
     # smollm3: every `no_rope_step`-th layer attends without rotary position encoding (`llama.cpp/src/models/smollm3.cpp:26`)
     no_rope_step: int = 0
@@ -263,6 +264,8 @@ PRESETS: dict[str, ModelConfig] = {
                                     n_ff=256, n_ctx_train=512, rope_theta=10000.0, rope_dim=32, rope_neox=True, fused_qkv=True, qk_norm=True, n_expert=8,
                                     n_expert_used=2, moe_norm_topk=True, n_ff_shared=256, n_layer_dense_lead=1, n_ff_dense=512, expert_weights_scale=2.5,
                                     moe_gating="sigmoid", moe_sel_bias=True, moe_scale_w=True, n_expert_groups=4, n_group_used=2),
+    "tiny-bitnet": ModelConfig(name="tiny-bitnet", arch="bitnet", vocab_size=512, n_embd=256, n_layer=2, n_head=4, n_head_kv=2, head_dim=64, n_ff=512,
+                               n_ctx_train=512, rope_theta=10000.0, rope_dim=64, rope_neox=True, sub_norm=True, tie_embeddings=True),
     "tiny-exaone4": ModelConfig(name="tiny-exaone4", arch="exaone4", vocab_size=512, n_embd=256, n_layer=2, n_head=4, n_head_kv=2, head_dim=64, n_ff=512,
                                 n_ctx_train=512, rope_theta=10000.0, rope_dim=64, rope_neox=True, qk_norm=True, post_norm=True, pre_norm=False),
     "tiny-command-r": ModelConfig(name="tiny-command-r", arch="command-r", vocab_size=512, n_embd=256, n_layer=2, n_head=4, n_head_kv=2,
@@ -304,7 +307,7 @@ PRESETS: dict[str, ModelConfig] = {
 SUPPORTED_ARCHS = {"llama", "qwen2", "qwen2moe", "qwen3", "qwen3moe", "phi3", "granite",
                    "internlm2", "xverse", "ernie4_5", "exaone", "seed_oss", "minicpm", "granitemoe", "smollm3",
                    "starcoder2", "falcon", "olmo", "orion", "command-r", "gptneox", "stablelm", "nemotron", "arcee",
-                   "gpt2", "starcoder", "codeshell", "qwen", "baichuan", "olmo2", "glm4", "mistral3", "pangu-embedded", "chatglm", "plamo", "deepseek", "bailingmoe", "qwen2vl", "qwen3vl", "exaone4", "phi2", "olmoe", "qwen3vlmoe", "glm4moe", "dots1", "ernie4_5-moe", "minimax-m2", "bailingmoe2"}
+                   "gpt2", "starcoder", "codeshell", "qwen", "baichuan", "olmo2", "glm4", "mistral3", "pangu-embedded", "chatglm", "plamo", "deepseek", "bailingmoe", "qwen2vl", "qwen3vl", "exaone4", "phi2", "olmoe", "qwen3vlmoe", "glm4moe", "dots1", "ernie4_5-moe", "minimax-m2", "bailingmoe2", "bitnet"}
 ROPE_NORM_ARCHS = {"llama", "granite", "granitemoe", "minicpm", "internlm2", "xverse", "ernie4_5", "ernie4_5-moe", "smollm3", "olmo", "command-r", "arcee", "baichuan", "glm4", "mistral3", "chatglm", "deepseek", "bailingmoe"}     # llama_model_rope_type
 # LayerNorm families and what differs beyond the norm (llama.cpp/src/models/{starcoder2,falcon,olmo,orion,command-r}.cpp):
 #   starcoder2: biases on every matrix, non-gated GELU MLP;  falcon: fused QKV, GELU MLP, attention and MLP in parallel from the same
@@ -360,6 +363,8 @@ def config_from_gguf(meta: dict[str, Any], tensors: dict | None = None) -> Model
     n_layer = int(g("block_count")) - int(g("nextn_predict_layers", 0) or 0)      # trailing multi-token-prediction layers are not part of the forward pass (glm4-moe.cpp:24)
     if arch == "exaone4" and (n_layer == 64 or int(g("attention.sliding_window", 0) or 0) > 0):
         raise NotImplementedError("exaone4 checkpoints with sliding-window layers (the 32B model) are not supported")
+    if arch == "bitnet" and tensors is not None and any(k.endswith(".scale") for k in tensors):
+        raise NotImplementedError("bitnet files with separate per-matrix scale tensors (I2_S exports) are not supported: use a TQ1_0 / TQ2_0 / F16 file")
     if arch == "mistral3" and float(g("attention.temperature_scale", 0.0) or 0.0) != 0.0:
         raise NotImplementedError("mistral3 checkpoints with a position-dependent attention temperature are not supported")
     if tensors is not None and "blk.0.ffn_down.weight" in tensors and int(g("feed_forward_length")) // (2 if arch == "qwen" else 1) != tensors["blk.0.ffn_down.weight"].shape[-1]:
@@ -387,7 +392,7 @@ def config_from_gguf(meta: dict[str, Any], tensors: dict | None = None) -> Model
         moe_gating="sigmoid" if ((arch == "glm4moe" and int(g("expert_gating_func", 0) or 0) in (0, 2)) or (arch in ("dots1", "minimax-m2", "bailingmoe2") and int(g("expert_gating_func", 0) or 0) == 2)) else "softmax",
         moe_sel_bias=tensors is not None and any(k.endswith(".exp_probs_b.bias") for k in tensors), moe_scale_w=arch in ("glm4moe", "dots1", "bailingmoe2"),
         n_expert_groups=int(g("expert_group_count", 0) or 0), n_group_used=int(g("expert_group_used_count", 0) or 0),
-        moe_layer_step=int(g("interleave_moe_layer_step", 1) or 1),
+        moe_layer_step=int(g("interleave_moe_layer_step", 1) or 1), sub_norm=arch == "bitnet",
         moe_norm_topk=bool(g("expert_weights_norm", False)) if arch in ("bailingmoe", "glm4moe", "dots1", "bailingmoe2") else arch not in ("qwen2moe", "deepseek", "olmoe"),
         n_ff_shared=(int(g("expert_shared_feed_forward_length", 0) or g("expert_feed_forward_length")) * int(g("expert_shared_count", 1) or 1)) if arch == "bailingmoe2" else
         int(g("expert_shared_feed_forward_length", 0) or 0) or (int(g("expert_shared_count", 0) or 0) * int(g("expert_feed_forward_length", 0) or 0)),

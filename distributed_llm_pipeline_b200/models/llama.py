@@ -387,6 +387,9 @@ class LlamaEngine:
                 qkv[:, sl] = (v * torch.rsqrt(v.pow(2).mean(-1, keepdim=True) + cfg.rms_eps) * wn).to(qkv.dtype)
         q = self._rope(il, qkv, T)
         att = attn_fn(il, q, T)
+        if lw.attn_sub_norm is not None:                           # bitnet: RMSNorm over the attention result, in front of the output matrix
+            v = att.float()
+            att = (v * torch.rsqrt(v.pow(2).mean(-1, keepdim=True) + cfg.rms_eps) * lw.attn_sub_norm).to(att.dtype)
         d = ops.linear(lw.wo, att, "f32", out=self.delta[:T], scratch=self._scratch_for(lw.wo))
         if tp:
             d = comm.allreduce_delta(d, il, 0)
@@ -408,6 +411,9 @@ class LlamaEngine:
             act = ops.bias_act(up, lw.b_up, cfg.ffn_act, out=self.act[:T])
         else:
             act = ops.linear(lw.w_gate, ffn_in, "swiglu", w_up=lw.w_up, out=self.act[:T], scratch=self._scratch_for(lw.w_gate, lw.w_up))
+        if lw.ffn_sub_norm is not None:                            # bitnet: RMSNorm over the gated activation, in front of the down matrix
+            v = act.float()
+            act = (v * torch.rsqrt(v.pow(2).mean(-1, keepdim=True) + cfg.rms_eps) * lw.ffn_sub_norm).to(act.dtype)
         d = ops.linear(lw.w_down, act, "f32", out=self.delta[:T], scratch=self._scratch_for(lw.w_down))
         if tp:
             d = comm.allreduce_delta(d, il, 1)

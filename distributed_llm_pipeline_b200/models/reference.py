@@ -177,6 +177,8 @@ class ReferenceModel:
         scores = scores.masked_fill(mask[None], float("-inf"))
         att = torch.softmax(scores, dim=-1)
         o = torch.einsum("hts,shd->thd", att, Vx).reshape(T, c.q_dim)
+        if p + "attn_sub_norm.weight" in w:       # bitnet: the attention result is normalised before the output matrix
+            o = rms_norm(o, w[p + "attn_sub_norm.weight"], c.rms_eps)
         out = self.mm(o, p + "attn_output.weight")
         return out + w[p + "attn_output.bias"] if p + "attn_output.bias" in w else out
 
@@ -196,7 +198,10 @@ class ReferenceModel:
         if not c.is_moe or p + "ffn_gate_inp.weight" not in w:      # dense model, or one of the dense lead layers of deepseek / bailingmoe
             g = self.mm(x, p + "ffn_gate.weight")
             u = self.mm(x, p + "ffn_up.weight")
-            return self.mm(torch.nn.functional.silu(g) * u, p + "ffn_down.weight")
+            a = torch.nn.functional.silu(g) * u
+            if p + "ffn_sub_norm.weight" in w:    # bitnet
+                a = rms_norm(a, w[p + "ffn_sub_norm.weight"], c.rms_eps)
+            return self.mm(a, p + "ffn_down.weight")
         logits = self.mm(x, p + "ffn_gate_inp.weight")
         probs = torch.sigmoid(logits) if c.moe_gating == "sigmoid" else torch.softmax(logits, dim=-1)
         sel = probs + w[p + "exp_probs_b.bias"] if p + "exp_probs_b.bias" in w else probs     # the bias steers which experts are picked ...

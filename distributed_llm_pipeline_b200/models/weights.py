@@ -36,6 +36,8 @@ class LayerWeights:
     # MoE
     router: torch.Tensor | None = None                 # fp32 [n_expert, E]
     shared_gate: torch.Tensor | None = None            # fp32 [E]: sigmoid gate of the shared expert (qwen2moe; w_gate/w_up/w_down hold it)
+    attn_sub_norm: torch.Tensor | None = None          # bitnet: fp32 [q_dim] / [n_ff] RMSNorm weights in front of wo / w_down
+    ffn_sub_norm: torch.Tensor | None = None
     sel_bias: torch.Tensor | None = None               # fp32 [n_expert]: added to the router scores for the expert selection only (glm4moe)
     e_gate: list[DeviceWeight] = field(default_factory=list)
     e_up: list[DeviceWeight] = field(default_factory=list)
@@ -263,6 +265,10 @@ def load_weights(src: str | GGUFModelFiles, device, layer_range: range | None = 
             lw.attn_norm2, lw.attn_norm2_b = opt(p + "attn_norm_2.weight"), opt(p + "attn_norm_2.bias")
             lw.bo, lw.b_down = opt(p + "attn_output.bias"), opt(p + "ffn_down.bias")
             lw.post_attn_norm, lw.post_ffn_norm = opt(p + "post_attention_norm.weight"), opt(p + "post_ffw_norm.weight")
+            if cfg.sub_norm:
+                if tp_size > 1:
+                    raise NotImplementedError("bitnet's sub-norms span the full attention / MLP width: not split across tensor-parallel ranks")
+                lw.attn_sub_norm, lw.ffn_sub_norm = f32(p + "attn_sub_norm.weight"), f32(p + "ffn_sub_norm.weight")
             if cfg.qk_norm_full:
                 if tp_size > 1:
                     raise NotImplementedError("Q/K norms over the full projected width (olmo2) are not split across tensor-parallel ranks")

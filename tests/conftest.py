@@ -33,7 +33,7 @@ def tmp_models(tmp_path_factory):
                         ("tiny-granite", "Q8_0"), ("tiny-granite", "Q4_K_M"), ("tiny-tp8", "F16"), ("tiny-moe-tp", "F16"), ("tiny-moe-tp", "Q8_0")] + \
             [(n, "F16") for n in ("tiny-internlm2", "tiny-xverse", "tiny-ernie", "tiny-exaone", "tiny-seed-oss", "tiny-minicpm", "tiny-granitemoe", "tiny-smollm3",
                                        "tiny-starcoder2", "tiny-falcon", "tiny-olmo", "tiny-orion", "tiny-command-r", "tiny-gptneox", "tiny-stablelm", "tiny-nemotron", "tiny-arcee",
-                                       "tiny-gpt2", "tiny-starcoder", "tiny-codeshell", "tiny-qwen", "tiny-olmo2", "tiny-glm4", "tiny-mistral3", "tiny-pangu", "tiny-chatglm", "tiny-plamo", "tiny-deepseek", "tiny-bailingmoe", "tiny-qwen2vl", "tiny-qwen3vl", "tiny-exaone4", "tiny-phi2", "tiny-olmoe", "tiny-qwen3vlmoe", "tiny-glm4moe", "tiny-dots1", "tiny-ernie-moe", "tiny-minimax-m2", "tiny-bailingmoe2")] + \
+                                       "tiny-gpt2", "tiny-starcoder", "tiny-codeshell", "tiny-qwen", "tiny-olmo2", "tiny-glm4", "tiny-mistral3", "tiny-pangu", "tiny-chatglm", "tiny-plamo", "tiny-deepseek", "tiny-bailingmoe", "tiny-qwen2vl", "tiny-qwen3vl", "tiny-exaone4", "tiny-phi2", "tiny-olmoe", "tiny-qwen3vlmoe", "tiny-glm4moe", "tiny-dots1", "tiny-ernie-moe", "tiny-minimax-m2", "tiny-bailingmoe2", "tiny-bitnet")] + \
             [("tiny-smollm3", "Q8_0"), ("tiny-starcoder2", "Q8_0"), ("tiny-falcon", "Q8_0"), ("tiny-gptneox", "Q8_0")]:
         out[(name, ftype)] = write_synthetic_gguf(str(root / f"{name}-{ftype}.gguf"), preset(name), ftype, seed=1)
     return out

@@ -104,7 +104,9 @@ CASES = [("tiny", "F16", 4e-3, 8e-4), ("tiny", "Q8_0", 5e-2, 8e-3), ("tiny", "Q4
          ("tiny-phi2", "F16", 4e-3, 8e-4), ("tiny-olmoe", "F16", 4e-3, 8e-4), ("tiny-qwen3vlmoe", "F16", 1.2e-2, 1.6e-3),
          # DeepSeek-V3 style routing (sigmoid scores, selection bias, scaled weights), dense lead layers, ungated shared experts
          ("tiny-glm4moe", "F16", 4e-3, 8e-4), ("tiny-dots1", "F16", 4e-3, 8e-4), ("tiny-ernie-moe", "F16", 4e-3, 8e-4),
-         ("tiny-minimax-m2", "F16", 4e-3, 8e-4), ("tiny-bailingmoe2", "F16", 4e-3, 8e-4)]
+         ("tiny-minimax-m2", "F16", 4e-3, 8e-4), ("tiny-bailingmoe2", "F16", 4e-3, 8e-4),
+         # bitnet: sub-norms in front of the attention output and MLP down matrices; with its ternary storage too
+         ("tiny-bitnet", "F16", 4e-3, 8e-4), ("tiny-bitnet", "TQ2_0", 8e-2, 1.5e-2)]
 
 
 @pytest.mark.parametrize("name,ftype,tol_max,tol_mean", CASES, ids=[f"{n}-{f}" for n, f, _, _ in CASES])

@@ -76,7 +76,7 @@ def test_rope_modes():
                                  ("tiny-olmo2", "F16"), ("tiny-glm4", "F16"), ("tiny-mistral3", "F16"), ("tiny-pangu", "F16"), ("tiny-chatglm", "F16"), ("tiny-plamo", "F16"),
                                  ("tiny-deepseek", "F16"), ("tiny-bailingmoe", "F16"), ("tiny-qwen2vl", "F16"), ("tiny-qwen3vl", "F16"), ("tiny-exaone4", "F16"),
                                  ("tiny-phi2", "F16"), ("tiny-olmoe", "F16"), ("tiny-qwen3vlmoe", "F16"),
-                                 ("tiny-glm4moe", "F16"), ("tiny-dots1", "F16"), ("tiny-ernie-moe", "F16"), ("tiny-minimax-m2", "F16"), ("tiny-bailingmoe2", "F16")])      # dense lead layers, shared experts without a gate        # branch outputs normalised before the residual add
+                                 ("tiny-glm4moe", "F16"), ("tiny-dots1", "F16"), ("tiny-ernie-moe", "F16"), ("tiny-minimax-m2", "F16"), ("tiny-bailingmoe2", "F16"), ("tiny-bitnet", "F16")])      # dense lead layers, shared experts without a gate        # branch outputs normalised before the residual add
 def test_other_architectures_match_oracle_cpu(tmp_models, key):
     """qwen2 (QKV bias), qwen3 (per-head Q/K norm) and phi3 (fused QKV / gate-up tensors), all with half-split RoPE:
     engine (CPU op fallbacks, paged KV) against the fp32 oracle."""

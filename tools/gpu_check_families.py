@@ -22,7 +22,7 @@ FAMILIES = [("tiny-starcoder2", "F16"), ("tiny-starcoder2", "Q8_0"), ("tiny-falc
             ("tiny-command-r", "F16"), ("tiny-gptneox", "F16"), ("tiny-gptneox", "Q8_0"), ("tiny-stablelm", "F16"), ("tiny-nemotron", "F16"),
             ("tiny-arcee", "F16"), ("tiny-smollm3", "F16"), ("tiny-smollm3", "Q8_0"), ("tiny-internlm2", "F16"), ("tiny-exaone", "F16"),
             ("tiny-seed-oss", "F16"), ("tiny-minicpm", "F16"), ("tiny-granitemoe", "F16"), ("tiny-gpt2", "F16"), ("tiny-starcoder", "F16"),
-            ("tiny-codeshell", "F16"), ("tiny-qwen", "F16"), ("tiny-olmo2", "F16"), ("tiny-glm4", "F16"), ("tiny-mistral3", "F16"), ("tiny-pangu", "F16"), ("tiny-chatglm", "F16"), ("tiny-plamo", "F16"), ("tiny-deepseek", "F16"), ("tiny-bailingmoe", "F16"), ("tiny-qwen2vl", "F16"), ("tiny-qwen3vl", "F16"), ("tiny-exaone4", "F16"), ("tiny-phi2", "F16"), ("tiny-olmoe", "F16"), ("tiny-qwen3vlmoe", "F16"), ("tiny-glm4moe", "F16"), ("tiny-dots1", "F16"), ("tiny-ernie-moe", "F16"), ("tiny-minimax-m2", "F16"), ("tiny-bailingmoe2", "F16")]
+            ("tiny-codeshell", "F16"), ("tiny-qwen", "F16"), ("tiny-olmo2", "F16"), ("tiny-glm4", "F16"), ("tiny-mistral3", "F16"), ("tiny-pangu", "F16"), ("tiny-chatglm", "F16"), ("tiny-plamo", "F16"), ("tiny-deepseek", "F16"), ("tiny-bailingmoe", "F16"), ("tiny-qwen2vl", "F16"), ("tiny-qwen3vl", "F16"), ("tiny-exaone4", "F16"), ("tiny-phi2", "F16"), ("tiny-olmoe", "F16"), ("tiny-qwen3vlmoe", "F16"), ("tiny-glm4moe", "F16"), ("tiny-dots1", "F16"), ("tiny-ernie-moe", "F16"), ("tiny-minimax-m2", "F16"), ("tiny-bailingmoe2", "F16"), ("tiny-bitnet", "F16")]
 PROMPT = [1, 5, 9, 200, 33, 7, 8, 100, 42, 17, 3, 250, 77]
 
 
