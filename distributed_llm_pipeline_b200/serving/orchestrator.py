@@ -624,7 +624,22 @@ class Orchestrator:
             await self._stream_request(req, writer, fmt)
             return False
         await self._run_blocking(req)
-        await self._json(writer, self._openai_text(req, rid) if openai else self._native_final(req, d))
+        out = self._openai_text(req, rid) if openai else self._native_final(req, d)
+        fields = d.get("response_fields")
+        if not openai and isinstance(fields, list) and fields:      # only these fields, nested ones by path ("timings/prompt_n"), keyed by the path
+            picked = {}
+            for path in fields:
+                cur, ok = out, True
+                for k in str(path).split("/"):
+                    if isinstance(cur, dict) and k in cur:
+                        cur = cur[k]
+                    else:
+                        ok = False
+                        break
+                if ok:
+                    picked[str(path)] = cur
+            out = picked
+        await self._json(writer, out)
         return True
 
     async def rerank(self, d: dict, writer) -> bool:

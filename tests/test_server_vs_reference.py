@@ -427,11 +427,15 @@ def test_response_envelopes_carry_every_field_of_the_reference(pair):
              ("/v1/completions", {"prompt": "one two three", "max_tokens": 4, "temperature": 0}),
              ("/v1/completions", {"prompt": "one two three", "max_tokens": 4, "temperature": 0, "logprobs": 2}),
              ("/v1/chat/completions", {"messages": [{"role": "user", "content": "hi"}], "max_tokens": 4, "temperature": 0, "logprobs": True, "top_logprobs": 2}),
+             ("/completion", {"prompt": "one two", "n_predict": 2, "temperature": 0, "cache_prompt": False,
+                              "response_fields": ["content", "timings/prompt_n", "generation_settings/n_predict", "nope/x"]}),
              ("/tokenize", {"content": "hello wörld", "with_pieces": True}), ("/tokenize", {"content": "hello", "add_special": True})]
     for path, body in cases:
         (sa, a), (sb, b) = _status(ours, path, body), _status(ref, path, body)
         assert sa == sb == 200, (path, body, a, b)
         assert _keys(b) - _keys(a) == set(), (path, body, sorted(_keys(b) - _keys(a)))
+        if "response_fields" in body:
+            assert set(a) == set(b) == {"content", "timings/prompt_n", "generation_settings/n_predict"} and a["generation_settings/n_predict"] == 2
         if isinstance(b, list):       # an array of prompts: one record each (the reference lists them as they finish: pair them by prompt)
             assert len(a) == len(b) == len(body["prompt"]) and sorted(x["index"] for x in a) == sorted(y["index"] for y in b)
             a, b = sorted(a, key=lambda r: r["prompt"]), sorted(b, key=lambda r: r["prompt"])
